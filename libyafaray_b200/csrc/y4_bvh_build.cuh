@@ -1,0 +1,122 @@
+// Binary LBVH construction, per-element logic (Y4_HD so the unit-test emulation can run it).
+//
+// Replaces the reference's serial SAH kd-tree build
+// (/root/reference/src/accelerator/accelerator_kdtree.cc:47-123,420-628) with a
+// data-parallel pipeline: triangle AABBs -> 63-bit Morton keys -> radix sort ->
+// Karras 2012 hierarchy (one thread per internal node) -> bottom-up refit.
+// The binary tree is only an intermediate: y4_bvh8.cuh collapses it to the
+// compressed 8-wide BVH the traversal kernels walk.
+//
+// Node index space: [0, n-1) internal nodes, [n-1, 2n-1) leaves (leaf k == sorted
+// triangle k).  Boxes are float4 pairs (w unused) so kernels move them as 128-bit words.
+#pragma once
+#include "y4_common.cuh"
+
+struct Y4Box { float lox, loy, loz, hix, hiy, hiz; };
+
+Y4_HD Y4Box y4_box_empty()
+{
+	Y4Box b; b.lox = b.loy = b.loz = FLT_MAX; b.hix = b.hiy = b.hiz = -FLT_MAX; return b;
+}
+Y4_HD Y4Box y4_box_union(const Y4Box &a, const Y4Box &b)
+{
+	Y4Box r;
+	r.lox = fminf(a.lox, b.lox); r.loy = fminf(a.loy, b.loy); r.loz = fminf(a.loz, b.loz);
+	r.hix = fmaxf(a.hix, b.hix); r.hiy = fmaxf(a.hiy, b.hiy); r.hiz = fmaxf(a.hiz, b.hiz);
+	return r;
+}
+Y4_HD float y4_box_half_area(const Y4Box &b)
+{
+	const float dx = b.hix - b.lox, dy = b.hiy - b.loy, dz = b.hiz - b.loz;
+	return dx * dy + dy * dz + dz * dx;
+}
+// Exact min/max of the three vertices (reference FacePrimitive::getBound, primitive_face.cc:113-128).
+Y4_HD Y4Box y4_tri_box(const float *v)
+{
+	Y4Box b;
+	b.lox = fminf(v[0], fminf(v[3], v[6])); b.hix = fmaxf(v[0], fmaxf(v[3], v[6]));
+	b.loy = fminf(v[1], fminf(v[4], v[7])); b.hiy = fmaxf(v[1], fmaxf(v[4], v[7]));
+	b.loz = fminf(v[2], fminf(v[5], v[8])); b.hiz = fmaxf(v[2], fmaxf(v[5], v[8]));
+	return b;
+}
+
+// Spread the low 21 bits of x so that there are two zero bits between each.
+Y4_HD uint64_t y4_expand21(uint64_t x)
+{
+	x &= 0x1fffffull;
+	x = (x | x << 32) & 0x1f00000000ffffull;
+	x = (x | x << 16) & 0x1f0000ff0000ffull;
+	x = (x | x << 8) & 0x100f00f00f00f00full;
+	x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+	x = (x | x << 2) & 0x1249249249249249ull;
+	return x;
+}
+// 63-bit Morton key of a centroid normalised to the scene box.
+Y4_HD uint64_t y4_morton63(const Y4Box &tri, const Y4Box &scene)
+{
+	const float ex = scene.hix - scene.lox, ey = scene.hiy - scene.loy, ez = scene.hiz - scene.loz;
+	const float cx = 0.5f * (tri.lox + tri.hix), cy = 0.5f * (tri.loy + tri.hiy), cz = 0.5f * (tri.loz + tri.hiz);
+	float nx = ex > 0.f ? (cx - scene.lox) / ex : 0.f;
+	float ny = ey > 0.f ? (cy - scene.loy) / ey : 0.f;
+	float nz = ez > 0.f ? (cz - scene.loz) / ez : 0.f;
+	nx = fminf(fmaxf(nx, 0.f), 1.f); ny = fminf(fmaxf(ny, 0.f), 1.f); nz = fminf(fmaxf(nz, 0.f), 1.f);
+	const uint64_t qx = (uint64_t) fminf(nx * 2097152.f, 2097151.f);
+	const uint64_t qy = (uint64_t) fminf(ny * 2097152.f, 2097151.f);
+	const uint64_t qz = (uint64_t) fminf(nz * 2097152.f, 2097151.f);
+	return (y4_expand21(qx) << 2) | (y4_expand21(qy) << 1) | y4_expand21(qz);
+}
+
+Y4_HD int y4_clz64(uint64_t x)
+{
+#if defined(__CUDA_ARCH__)
+	return __clzll((long long) x);
+#else
+	return x ? __builtin_clzll(x) : 64;
+#endif
+}
+Y4_HD int y4_clz32(uint32_t x)
+{
+#if defined(__CUDA_ARCH__)
+	return __clz((int) x);
+#else
+	return x ? __builtin_clz(x) : 32;
+#endif
+}
+
+// Karras' delta: common-prefix length of keys i and j, ties broken by index; -1 outside [0,n).
+Y4_HD int y4_delta(const uint64_t *keys, int n, int i, int j)
+{
+	if(j < 0 || j >= n) return -1;
+	const uint64_t x = keys[i] ^ keys[j];
+	if(x == 0) return 64 + y4_clz32((uint32_t) i ^ (uint32_t) j);
+	return y4_clz64(x);
+}
+
+// One internal node of the Karras hierarchy.  Writes its children, their parent links and
+// the sorted-leaf range [first, last] it covers.
+Y4_HD void y4_karras_node(const uint64_t *keys, int n, int i, int *left, int *right, int *parent, int *range_first, int *range_last)
+{
+	const int d = (y4_delta(keys, n, i, i + 1) - y4_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+	const int dmin = y4_delta(keys, n, i, i - d);
+	int lmax = 2;
+	while(y4_delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+	int l = 0;
+	for(int t = lmax >> 1; t >= 1; t >>= 1)
+		if(y4_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+	const int j = i + l * d;
+	const int dnode = y4_delta(keys, n, i, j);
+	int s = 0;
+	for(int t = (l + 1) >> 1; ; t = (t + 1) >> 1)
+	{
+		if(y4_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+		if(t <= 1) break;
+	}
+	const int gamma = i + s * d + (d < 0 ? -1 : 0);
+	const int lo = i < j ? i : j, hi = i < j ? j : i;
+	const int lc = (lo == gamma) ? (n - 1 + gamma) : gamma;
+	const int rc = (hi == gamma + 1) ? (n - 1 + gamma + 1) : (gamma + 1);
+	left[i] = lc; right[i] = rc;
+	parent[lc] = i; parent[rc] = i;
+	range_first[i] = lo; range_last[i] = hi;
+	if(i == 0) parent[0] = -1;
+}

@@ -1,0 +1,120 @@
+// UNIT-TEST EMULATION ONLY.  Compiles the Y4_HD per-element logic of
+// libyafaray_b200/csrc/*.cuh with g++ and runs the "kernels" as serial loops, so the BVH
+// builder / BVH8 encoder / traversal logic can be debugged on a machine without a GPU.
+// Never linked into liby4gpu.so; the product path has no CPU fallback.
+#include "../../libyafaray_b200/csrc/y4_trace.cuh"
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+struct EmuBvh
+{
+	std::vector<Y4U4> nodes;
+	std::vector<Y4Tri> tris;
+	uint32_t n_nodes = 0;
+	int n = 0;
+};
+
+static void build(const float *verts, const uint32_t *flags, int n, int leaf_max, EmuBvh &out)
+{
+	out.n = n;
+	if(n == 0) return;
+	std::vector<Y4Box> tb(n);
+	Y4Box scene = y4_box_empty();
+	for(int i = 0; i < n; ++i) { tb[i] = y4_tri_box(verts + 9ull * i); scene = y4_box_union(scene, tb[i]); }
+	std::vector<std::pair<uint64_t, uint32_t>> kv(n);
+	for(int i = 0; i < n; ++i) kv[i] = {y4_morton63(tb[i], scene), (uint32_t) i};
+	std::stable_sort(kv.begin(), kv.end(), [](const std::pair<uint64_t, uint32_t> &a, const std::pair<uint64_t, uint32_t> &b) { return a.first < b.first; });
+	std::vector<uint64_t> keys(n);
+	std::vector<uint32_t> sorted_prim(n);
+	for(int i = 0; i < n; ++i) { keys[i] = kv[i].first; sorted_prim[i] = kv[i].second; }
+	const int n_int = n > 1 ? n - 1 : 0;
+	std::vector<int> left(n_int + 1), right(n_int + 1), first(n_int + 1), last(n_int + 1), parent(2 * n), flag(n_int + 1, 0);
+	std::vector<Y4Box> box(2 * n);
+	for(int i = 0; i < n_int; ++i) y4_karras_node(keys.data(), n, i, left.data(), right.data(), parent.data(), first.data(), last.data());
+	for(int k = 0; k < n; ++k) box[n - 1 + k] = tb[sorted_prim[k]];
+	// bottom-up refit, second arrival proceeds
+	for(int k = 0; k < n && n > 1; ++k)
+	{
+		int cur = parent[n - 1 + k];
+		while(cur >= 0)
+		{
+			if(flag[cur]++ == 0) break;
+			box[cur] = y4_box_union(box[left[cur]], box[right[cur]]);
+			cur = parent[cur];
+		}
+	}
+	Y4BinTree bt;
+	bt.n = n; bt.left = left.data(); bt.right = right.data(); bt.first = first.data(); bt.last = last.data();
+	bt.box = box.data(); bt.sorted_prim = sorted_prim.data();
+	out.nodes.assign((size_t) std::max(1, n) * Y4_NODE_WORDS, Y4U4{0, 0, 0, 0});
+	out.tris.resize(n);
+	uint32_t node_counter = 1, tri_counter = 0;
+	std::vector<uint32_t> cur_items{0u, 0u}, next_items(2 * (size_t) n + 2);
+	uint32_t cur_count = 1;
+	while(cur_count)
+	{
+		uint32_t next_count = 0;
+		Y4CollapseOut co;
+		co.nodes = out.nodes.data(); co.tris = out.tris.data(); co.node_counter = &node_counter; co.tri_counter = &tri_counter;
+		co.next_items = next_items.data(); co.next_count = &next_count;
+		for(uint32_t i = 0; i < cur_count; ++i) y4_collapse_item(bt, leaf_max, cur_items[2 * i], cur_items[2 * i + 1], verts, flags, co);
+		cur_items.assign(next_items.begin(), next_items.begin() + 2 * (size_t) next_count);
+		cur_count = next_count;
+	}
+	out.n_nodes = node_counter;
+	if(tri_counter != (uint32_t) n) fprintf(stderr, "emu: tri_counter %u != n %d\n", tri_counter, n);
+}
+
+extern "C" {
+
+// Build + trace; returns number of wide nodes.  stats_out (nullable) = [sum nodes visited, sum tris tested].
+int emu_build_trace(const float *verts, const uint32_t *flags, int n, const float *rays, int m, int kind, int leaf_max,
+                    Y4Hit *hits, uint64_t *stats_out)
+{
+	EmuBvh b;
+	build(verts, flags, n, leaf_max, b);
+	Y4Bvh8 bvh; bvh.nodes = b.nodes.data(); bvh.tris = b.tris.data(); bvh.n_tris = (uint32_t) n;
+	uint64_t sn = 0, st = 0;
+	for(int i = 0; i < m; ++i)
+	{
+		Y4Ray r; memcpy(&r, rays + 8ull * i, sizeof(r));
+		const Y4PreparedRay pr = y4_prepare_ray(r, kind);
+		uint2 stack[Y4_STACK_SIZE];
+		uint32_t filt[16]; int n_filt = 0;
+		Y4TraceStats s{0, 0};
+		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray<Y4_TRACE_CLOSEST>(bvh, pr, hits[i], stack, &s, filt, &n_filt, 0);
+		else if(kind == Y4_TRACE_SHADOW) y4_trace_ray<Y4_TRACE_SHADOW>(bvh, pr, hits[i], stack, &s, filt, &n_filt, 0);
+		else y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, hits[i], stack, &s, filt, &n_filt, 8);
+		sn += s.nodes; st += s.tris;
+	}
+	if(stats_out) { stats_out[0] = sn; stats_out[1] = st; }
+	return (int) b.n_nodes;
+}
+
+// Brute force over all triangles in primitive order with the same exact triangle test.
+void emu_brute(const float *verts, const uint32_t *flags, int n, const float *rays, int m, int kind, Y4Hit *hits)
+{
+	std::vector<Y4Tri> tr(n);
+	for(int i = 0; i < n; ++i) tr[i] = y4_tri_setup(verts + 9ull * i, (uint32_t) i, flags ? flags[i] : (uint32_t) Y4_TRI_DEFAULT_FLAGS);
+	const uint32_t vis = kind == Y4_TRACE_CLOSEST ? Y4_TRI_VIS_CLOSEST : (kind == Y4_TRACE_SHADOW ? Y4_TRI_VIS_SHADOW : Y4_TRI_VIS_TSHADOW);
+	for(int i = 0; i < m; ++i)
+	{
+		Y4Ray r; memcpy(&r, rays + 8ull * i, sizeof(r));
+		const Y4PreparedRay pr = y4_prepare_ray(r, kind);
+		Y4Hit h{0.f, 0.f, 0.f, -1};
+		float t_hi = pr.t_hi;
+		for(int k = 0; k < n; ++k)
+		{
+			float t, u, v;
+			if(!y4_tri_intersect(pr.o, pr.d, v3(tr[k].v0x, tr[k].v0y, tr[k].v0z), v3(tr[k].e1x, tr[k].e1y, tr[k].e1z), v3(tr[k].e2x, tr[k].e2y, tr[k].e2z), tr[k].eps, t, u, v)) continue;
+			if(!(t < t_hi && t >= pr.t_lo) || !(tr[k].flags & vis)) continue;
+			h.t = t; h.bu = u; h.bv = v; h.prim = k;
+			if(kind != Y4_TRACE_CLOSEST) break;
+			t_hi = t;
+		}
+		hits[i] = h;
+	}
+}
+}
