@@ -1,0 +1,116 @@
+/* y4gpu.h -- C-ABI of the B200 ray-intersection / wavefront path-tracing back end.
+ *
+ * This is the drop-in boundary: the libYafaRay-side plugin classes (an Accelerator
+ * subtype registered in Accelerator::factory and a PathIntegrator back end, see
+ * INTEGRATION.md) bind exactly these entry points.  Plain C, POD structs, int return
+ * codes (0 = ok, <0 = error, text via y4gpu_last_error), no exceptions and no torch
+ * types cross the boundary.  The library has NO CPU fallback: every compute entry
+ * point fails with Y4GPU_ERR_CUDA when no sm_100 device is usable.
+ *
+ * Reference interfaces replaced (paths relative to the libYafaRay tree):
+ *   y4gpu_upload_triangles/_build <- AcceleratorKdTree ctor + buildTree
+ *                                    src/accelerator/accelerator_kdtree.cc:47-123,420-628
+ *                                    (primitive list gathered by Scene::updateObjects,
+ *                                    src/scene/scene.cc:1032-1052)
+ *   y4gpu_get_bound               <- Accelerator::getBound, include/accelerator/accelerator.h:62
+ *   y4gpu_trace(CLOSEST)          <- Accelerator::intersect(ray, t_max), accelerator.h:59,
+ *                                    accelerator_kdtree.cc:634-773, wrapper accelerator.cc:55-67
+ *   y4gpu_trace(SHADOW)           <- Accelerator::isShadowed(ray, bias) -> intersectS,
+ *                                    accelerator.cc:69-80, accelerator_kdtree.cc:775-904
+ *   y4gpu_trace(TSHADOW)          <- Accelerator::isShadowed(ray, depth, bias, camera) ->
+ *                                    intersectTs, accelerator.cc:82-94, accelerator_kdtree.cc:911-1061
+ *   y4gpu_pt_*                    <- PathIntegrator::integrate + TiledIntegrator::renderPass +
+ *                                    ImageFilm::addSample (see the pt section below)
+ */
+#ifndef Y4GPU_H
+#define Y4GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define Y4GPU_OK 0
+#define Y4GPU_ERR_ARG (-1)    /* bad argument / wrong call order */
+#define Y4GPU_ERR_CUDA (-2)   /* CUDA runtime failure or no device (no CPU fallback) */
+#define Y4GPU_ERR_UNSUPPORTED (-3) /* scene feature outside the supported set: rejected, never approximated */
+
+typedef struct y4gpu_ctx y4gpu_ctx;
+
+/* Ray exactly as the reference's Ray carries it (include/geometry/ray.h:47-51):
+ * tmax < 0 means unbounded.  The wrapper conventions of accelerator.cc:55-94 (shadow-ray
+ * origin advance by dir*tmin, t_max = tmax - 2*tmin) are applied on the device. */
+typedef struct y4gpu_ray { float ox, oy, oz, tmin, dx, dy, dz, tmax; } y4gpu_ray;
+
+/* prim = index into the primitive list given to y4gpu_upload_triangles (== position in
+ * the vector handed to Accelerator::factory), -1 on miss.  (bu, bv) are the Moller-Trumbore
+ * (u, v) == reference barycentric_v_ / barycentric_w_; barycentric_u_ = 1 - bu - bv
+ * (src/geometry/primitive/primitive_triangle.cc:66-68). */
+typedef struct y4gpu_hit { float t, bu, bv; int32_t prim; } y4gpu_hit;
+
+/* transparent-shadow result: hit.prim >= 0 => shadowed (opaque blocker or depth exceeded);
+ * otherwise filter = product of the transparency colours of the distinct transparent
+ * primitives crossed (AcceleratorTsIntersectData::transparent_color_). */
+typedef struct y4gpu_tshit { y4gpu_hit hit; float filter_r, filter_g, filter_b, pad; } y4gpu_tshit;
+
+enum { Y4GPU_TRACE_CLOSEST = 0, Y4GPU_TRACE_SHADOW = 1, Y4GPU_TRACE_TSHADOW = 2 };
+
+/* per-triangle flag word (visibility matrix of accelerator_kdtree.cc:733-737,869-873,1022) */
+#define Y4GPU_TRI_VIS_CLOSEST 1u
+#define Y4GPU_TRI_VIS_SHADOW 2u
+#define Y4GPU_TRI_VIS_TSHADOW 4u
+#define Y4GPU_TRI_TRANSPARENT 8u
+#define Y4GPU_TRI_MAT_SHIFT 8u
+
+typedef struct y4gpu_build_params
+{
+	int32_t leaf_max;     /* triangles per BVH8 leaf slot, 1..3 (0 = default) */
+	int32_t reserved[7];
+} y4gpu_build_params;
+
+typedef struct y4gpu_stats
+{
+	uint64_t n_tris, n_nodes;           /* BVH8 size */
+	uint64_t node_bytes, tri_bytes;     /* resident HBM footprint of the accelerator */
+	double build_ms;                    /* last y4gpu_build, device time */
+	double last_trace_ms;               /* last y4gpu_trace kernel time (CUDA events on the trace stream) */
+	uint64_t last_trace_rays;
+	uint64_t nodes_visited, tris_tested; /* filled by y4gpu_trace_counted only */
+	uint64_t kernel_launches;           /* kernels launched by this ctx since creation */
+} y4gpu_stats;
+
+/* lifetime ------------------------------------------------------------------------------ */
+int y4gpu_create(int device, y4gpu_ctx **out);
+void y4gpu_destroy(y4gpu_ctx *ctx);
+const char *y4gpu_last_error(const y4gpu_ctx *ctx);   /* ctx may be NULL: last create error */
+int y4gpu_device_count(void);
+
+/* pinned host buffers for callers that want async copies (optional) */
+void *y4gpu_host_alloc(uint64_t bytes);
+void y4gpu_host_free(void *p);
+
+/* geometry + build ---------------------------------------------------------------------- */
+/* v_xyz: n_tri*9 floats, world space (instances already flattened like
+ * PrimitiveInstance does per test, primitive_instance.cc:43-51), in primitive order.
+ * flags: n_tri words or NULL (all visible, opaque, material 0).  Host or device pointers. */
+int y4gpu_upload_triangles(y4gpu_ctx *ctx, const float *v_xyz, const uint32_t *flags, uint64_t n_tri);
+int y4gpu_build(y4gpu_ctx *ctx, const y4gpu_build_params *params /* nullable */);
+/* tree bound with the reference's 0.1 % inflation (accelerator_kdtree.cc:81-85): lo xyz, hi xyz */
+int y4gpu_get_bound(const y4gpu_ctx *ctx, float out_bound[6]);
+
+/* ray batches ---------------------------------------------------------------------------- */
+/* rays/out may each be host or device memory (detected); out has n records. */
+int y4gpu_trace(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out);
+/* same, plus per-batch node/triangle visit counters in y4gpu_stats (slower; for the roofline) */
+int y4gpu_trace_counted(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out);
+/* transparent shadows: mat_transparency = n_mat * 3 floats (Material::getTransparency colour) */
+int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth,
+                        const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out);
+int y4gpu_get_stats(const y4gpu_ctx *ctx, y4gpu_stats *out);
+int y4gpu_synchronize(y4gpu_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* Y4GPU_H */

@@ -1,0 +1,118 @@
+"""ctypes binding of the C-ABI in include/y4gpu.h (liby4gpu.so, built in-tree for sm_100a).
+
+There is no CPU fallback: if the shared library is missing or no CUDA device is usable,
+loading / context creation raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liby4gpu.so")
+
+OK, ERR_ARG, ERR_CUDA, ERR_UNSUPPORTED = 0, -1, -2, -3
+TRACE_CLOSEST, TRACE_SHADOW, TRACE_TSHADOW = 0, 1, 2
+TRI_VIS_CLOSEST, TRI_VIS_SHADOW, TRI_VIS_TSHADOW, TRI_TRANSPARENT, TRI_MAT_SHIFT = 1, 2, 4, 8, 8
+
+RAY_DTYPE = np.dtype([("o", "f4", 3), ("tmin", "f4"), ("d", "f4", 3), ("tmax", "f4")])
+HIT_DTYPE = np.dtype([("t", "f4"), ("bu", "f4"), ("bv", "f4"), ("prim", "i4")])
+TSHIT_DTYPE = np.dtype([("t", "f4"), ("bu", "f4"), ("bv", "f4"), ("prim", "i4"), ("filter", "f4", 3), ("pad", "f4")])
+
+
+class BuildParams(C.Structure):
+    _fields_ = [("leaf_max", C.c_int32), ("reserved", C.c_int32 * 7)]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("n_tris", C.c_uint64), ("n_nodes", C.c_uint64),
+        ("node_bytes", C.c_uint64), ("tri_bytes", C.c_uint64),
+        ("build_ms", C.c_double), ("last_trace_ms", C.c_double),
+        ("last_trace_rays", C.c_uint64),
+        ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
+        ("kernel_launches", C.c_uint64),
+    ]  # fmt: skip
+
+
+class Y4Error(RuntimeError):
+    pass
+
+
+_lib = None
+
+# every symbol include/y4gpu.h declares (checked by tests/test_cabi.py)
+EXPORTED = [
+    "y4gpu_create", "y4gpu_destroy", "y4gpu_last_error", "y4gpu_device_count",
+    "y4gpu_host_alloc", "y4gpu_host_free",
+    "y4gpu_upload_triangles", "y4gpu_build", "y4gpu_get_bound",
+    "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow",
+    "y4gpu_get_stats", "y4gpu_synchronize",
+]  # fmt: skip
+
+
+def lib() -> C.CDLL:
+    """Load liby4gpu.so (raises if it was not built: run `python -c 'import __graft_entry__ as g; g.build()'`)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise Y4Error(f"{LIB_PATH} is missing: the CUDA extension was not built and there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, u64, i32, u32 = C.c_void_p, C.c_uint64, C.c_int, C.c_uint32
+    L.y4gpu_create.argtypes = [i32, C.POINTER(vp)]
+    L.y4gpu_create.restype = i32
+    L.y4gpu_destroy.argtypes = [vp]
+    L.y4gpu_destroy.restype = None
+    L.y4gpu_last_error.argtypes = [vp]
+    L.y4gpu_last_error.restype = C.c_char_p
+    L.y4gpu_device_count.argtypes = []
+    L.y4gpu_device_count.restype = i32
+    L.y4gpu_host_alloc.argtypes = [u64]
+    L.y4gpu_host_alloc.restype = vp
+    L.y4gpu_host_free.argtypes = [vp]
+    L.y4gpu_host_free.restype = None
+    L.y4gpu_upload_triangles.argtypes = [vp, vp, vp, u64]
+    L.y4gpu_upload_triangles.restype = i32
+    L.y4gpu_build.argtypes = [vp, C.POINTER(BuildParams)]
+    L.y4gpu_build.restype = i32
+    L.y4gpu_get_bound.argtypes = [vp, C.POINTER(C.c_float * 6)]
+    L.y4gpu_get_bound.restype = i32
+    for name in ("y4gpu_trace", "y4gpu_trace_counted"):
+        f = getattr(L, name)
+        f.argtypes = [vp, i32, vp, u64, vp]
+        f.restype = i32
+    L.y4gpu_trace_tshadow.argtypes = [vp, vp, u64, i32, vp, u32, vp]
+    L.y4gpu_trace_tshadow.restype = i32
+    L.y4gpu_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.y4gpu_get_stats.restype = i32
+    L.y4gpu_synchronize.argtypes = [vp]
+    L.y4gpu_synchronize.restype = i32
+    _lib = L
+    return L
+
+
+def check(ctx, rc: int, what: str) -> None:
+    if rc != OK:
+        msg = lib().y4gpu_last_error(ctx)
+        raise Y4Error(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")
+
+
+def pinned_empty(n: int, dtype) -> np.ndarray:
+    """numpy array backed by page-locked host memory (freed when the array is collected)."""
+    dtype = np.dtype(dtype)
+    nbytes = max(1, n * dtype.itemsize)
+    L = lib()
+    p = L.y4gpu_host_alloc(nbytes)
+    if not p:
+        raise Y4Error("y4gpu_host_alloc failed")
+    buf = (C.c_char * nbytes).from_address(p)
+    arr = np.frombuffer(buf, dtype=dtype, count=n)
+
+    import weakref
+
+    weakref.finalize(buf, L.y4gpu_host_free, p)  # views keep `buf` alive through .base
+    return arr
+

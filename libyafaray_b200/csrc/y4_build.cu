@@ -1,0 +1,235 @@
+// GPU construction of the BVH8: triangle boxes -> Morton keys -> radix sort -> Karras
+// hierarchy -> refit -> level-synchronous collapse into compressed 8-wide nodes.
+// Replaces the reference's serial kd-tree build
+// (/root/reference/src/accelerator/accelerator_kdtree.cc:47-123,420-628).
+// Per-element logic lives in y4_bvh_build.cuh / y4_bvh8.cuh (shared with the unit-test
+// emulation); this file holds the kernels and the host orchestration.
+#include "y4_ctx.h"
+#include <cub/device/device_radix_sort.cuh>
+#include <vector>
+
+namespace {
+
+__device__ __forceinline__ uint32_t enc_f(float f)
+{
+	const uint32_t u = __float_as_uint(f);
+	return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+inline float dec_f(uint32_t e)
+{
+	const uint32_t u = (e & 0x80000000u) ? (e & 0x7fffffffu) : ~e;
+	float f; memcpy(&f, &u, 4); return f;
+}
+
+// 1. per-triangle boxes + scene bound (warp shuffle reduce, one atomic set per warp)
+__global__ void __launch_bounds__(256) k_tri_boxes(const float *__restrict__ verts, int n, Y4Box *__restrict__ tb, uint32_t *__restrict__ scene_enc)
+{
+	Y4Box acc = y4_box_empty();
+	for(int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+	{
+		float v[9];
+#pragma unroll
+		for(int k = 0; k < 9; ++k) v[k] = __ldg(verts + 9ull * i + k);
+		const Y4Box b = y4_tri_box(v);
+		tb[i] = b;
+		acc = y4_box_union(acc, b);
+	}
+#pragma unroll
+	for(int o = 16; o > 0; o >>= 1)
+	{
+		acc.lox = fminf(acc.lox, __shfl_xor_sync(0xffffffffu, acc.lox, o));
+		acc.loy = fminf(acc.loy, __shfl_xor_sync(0xffffffffu, acc.loy, o));
+		acc.loz = fminf(acc.loz, __shfl_xor_sync(0xffffffffu, acc.loz, o));
+		acc.hix = fmaxf(acc.hix, __shfl_xor_sync(0xffffffffu, acc.hix, o));
+		acc.hiy = fmaxf(acc.hiy, __shfl_xor_sync(0xffffffffu, acc.hiy, o));
+		acc.hiz = fmaxf(acc.hiz, __shfl_xor_sync(0xffffffffu, acc.hiz, o));
+	}
+	if((threadIdx.x & 31) == 0)
+	{
+		atomicMin(scene_enc + 0, enc_f(acc.lox)); atomicMin(scene_enc + 1, enc_f(acc.loy)); atomicMin(scene_enc + 2, enc_f(acc.loz));
+		atomicMax(scene_enc + 3, enc_f(acc.hix)); atomicMax(scene_enc + 4, enc_f(acc.hiy)); atomicMax(scene_enc + 5, enc_f(acc.hiz));
+	}
+}
+
+// 2. Morton keys
+__global__ void __launch_bounds__(256) k_morton(const Y4Box *__restrict__ tb, int n, Y4Box scene, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= n) return;
+	keys[i] = y4_morton63(tb[i], scene);
+	vals[i] = (uint32_t) i;
+}
+
+// 4. Karras hierarchy, one thread per internal node
+__global__ void __launch_bounds__(256) k_karras(const uint64_t *__restrict__ keys, int n, int *left, int *right, int *parent, int *first, int *last)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= n - 1) return;
+	y4_karras_node(keys, n, i, left, right, parent, first, last);
+}
+
+__device__ __forceinline__ Y4Box ld_box_cg(const Y4Box *p)
+{
+	const float *f = reinterpret_cast<const float *>(p);
+	Y4Box b;
+	b.lox = __ldcg(f + 0); b.loy = __ldcg(f + 1); b.loz = __ldcg(f + 2);
+	b.hix = __ldcg(f + 3); b.hiy = __ldcg(f + 4); b.hiz = __ldcg(f + 5);
+	return b;
+}
+
+// 5. leaf boxes + bottom-up refit; the second thread to reach a node owns it
+__global__ void __launch_bounds__(256) k_refit(int n, const uint32_t *__restrict__ sorted_prim, const Y4Box *__restrict__ tb, Y4Box *box,
+                                               const int *__restrict__ parent, const int *__restrict__ left, const int *__restrict__ right, int *flags)
+{
+	const int k = blockIdx.x * blockDim.x + threadIdx.x;
+	if(k >= n) return;
+	box[n - 1 + k] = tb[sorted_prim[k]];
+	if(n == 1) return;
+	int cur = parent[n - 1 + k];
+	while(cur >= 0)
+	{
+		__threadfence();
+		if(atomicAdd(flags + cur, 1) == 0) return;
+		const Y4Box a = ld_box_cg(box + left[cur]), b = ld_box_cg(box + right[cur]);
+		box[cur] = y4_box_union(a, b);
+		cur = parent[cur];
+	}
+}
+
+// 6. one collapse level
+__global__ void __launch_bounds__(128) k_collapse(Y4BinTree bt, int leaf_max, const uint32_t *__restrict__ items, uint32_t count,
+                                                  const float *__restrict__ verts, const uint32_t *__restrict__ tri_flags, Y4CollapseOut out)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= count) return;
+	y4_collapse_item(bt, leaf_max, items[2 * i], items[2 * i + 1], verts, tri_flags, out);
+}
+
+template<typename T> struct DevBuf
+{
+	T *p = nullptr;
+	~DevBuf() { if(p) cudaFree(p); }
+	cudaError_t alloc(size_t n) { return cudaMalloc(&p, (n ? n : 1) * sizeof(T)); }
+};
+
+} // namespace
+
+int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
+{
+	const int n = (int) ctx->n_tri;
+	cudaStream_t st = ctx->stream;
+	if(ctx->d_nodes) { cudaFree(ctx->d_nodes); ctx->d_nodes = nullptr; }
+	if(ctx->d_tris) { cudaFree(ctx->d_tris); ctx->d_tris = nullptr; }
+	ctx->n_nodes = 0;
+	for(int k = 0; k < 6; ++k) ctx->raw_bound[k] = ctx->bound[k] = 0.f;
+	if(n == 0) { ctx->built = true; return Y4GPU_OK; }
+	if(leaf_max < 1 || leaf_max > 3) { ctx->err = "leaf_max must be 1..3"; return Y4GPU_ERR_ARG; }
+
+	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+	DevBuf<Y4Box> tb, box;
+	DevBuf<uint32_t> scene_enc, vals_a, vals_b, counters, items_a, items_b;
+	DevBuf<uint64_t> keys_a, keys_b;
+	DevBuf<int> left, right, parent, first, last, flags;
+	DevBuf<char> sort_tmp;
+	Y4_CUDA(ctx, tb.alloc(n)); Y4_CUDA(ctx, box.alloc(2ull * n));
+	Y4_CUDA(ctx, scene_enc.alloc(6));
+	Y4_CUDA(ctx, keys_a.alloc(n)); Y4_CUDA(ctx, keys_b.alloc(n)); Y4_CUDA(ctx, vals_a.alloc(n)); Y4_CUDA(ctx, vals_b.alloc(n));
+	Y4_CUDA(ctx, left.alloc(n)); Y4_CUDA(ctx, right.alloc(n)); Y4_CUDA(ctx, first.alloc(n)); Y4_CUDA(ctx, last.alloc(n));
+	Y4_CUDA(ctx, parent.alloc(2ull * n)); Y4_CUDA(ctx, flags.alloc(n));
+	Y4_CUDA(ctx, counters.alloc(4));
+
+	const uint32_t enc_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+	Y4_CUDA(ctx, cudaMemcpyAsync(scene_enc.p, enc_init, sizeof(enc_init), cudaMemcpyHostToDevice, st));
+	const int tpb = 256;
+	const int grid_n = (n + tpb - 1) / tpb;
+	k_tri_boxes<<<min(grid_n, ctx->sm_count * 8), tpb, 0, st>>>(ctx->d_verts, n, tb.p, scene_enc.p);
+	uint32_t enc_out[6];
+	Y4_CUDA(ctx, cudaMemcpyAsync(enc_out, scene_enc.p, sizeof(enc_out), cudaMemcpyDeviceToHost, st));
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	Y4Box scene;
+	scene.lox = dec_f(enc_out[0]); scene.loy = dec_f(enc_out[1]); scene.loz = dec_f(enc_out[2]);
+	scene.hix = dec_f(enc_out[3]); scene.hiy = dec_f(enc_out[4]); scene.hiz = dec_f(enc_out[5]);
+	ctx->raw_bound[0] = scene.lox; ctx->raw_bound[1] = scene.loy; ctx->raw_bound[2] = scene.loz;
+	ctx->raw_bound[3] = scene.hix; ctx->raw_bound[4] = scene.hiy; ctx->raw_bound[5] = scene.hiz;
+	// reference tree bound inflation, accelerator_kdtree.cc:81-85 (double arithmetic, stored as float)
+	for(int a = 0; a < 3; ++a)
+	{
+		const double foo = (double) (ctx->raw_bound[3 + a] - ctx->raw_bound[a]) * 0.001;
+		ctx->bound[a] = (float) ((double) ctx->raw_bound[a] - foo);
+		ctx->bound[3 + a] = (float) ((double) ctx->raw_bound[3 + a] + foo);
+	}
+
+	k_morton<<<grid_n, tpb, 0, st>>>(tb.p, n, scene, keys_a.p, vals_a.p);
+	cub::DoubleBuffer<uint64_t> dk(keys_a.p, keys_b.p);
+	cub::DoubleBuffer<uint32_t> dv(vals_a.p, vals_b.p);
+	size_t tmp_bytes = 0;
+	Y4_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, n, 0, 63, st));
+	Y4_CUDA(ctx, sort_tmp.alloc(tmp_bytes));
+	Y4_CUDA(ctx, cub::DeviceRadixSort::SortPairs(sort_tmp.p, tmp_bytes, dk, dv, n, 0, 63, st));
+	const uint64_t *keys = dk.Current();
+	const uint32_t *sorted_prim = dv.Current();
+
+	Y4_CUDA(ctx, cudaMemsetAsync(flags.p, 0, sizeof(int) * (size_t) n, st));
+	Y4_CUDA(ctx, cudaMemsetAsync(parent.p, 0xff, sizeof(int) * 2ull * n, st));
+	if(n > 1) k_karras<<<(n - 1 + tpb - 1) / tpb, tpb, 0, st>>>(keys, n, left.p, right.p, parent.p, first.p, last.p);
+	k_refit<<<grid_n, tpb, 0, st>>>(n, sorted_prim, tb.p, box.p, parent.p, left.p, right.p, flags.p);
+
+	// collapse into BVH8
+	const uint64_t max_nodes = (uint64_t) n;   // every wide node below the root owns >= 1 binary internal node
+	Y4U4 *nodes = nullptr; Y4Tri *tris = nullptr;
+	Y4_CUDA(ctx, cudaMalloc(&nodes, max_nodes * Y4_NODE_WORDS * sizeof(Y4U4)));
+	if(cudaMalloc(&tris, (size_t) n * sizeof(Y4Tri)) != cudaSuccess) { cudaFree(nodes); ctx->err = "cudaMalloc tris failed"; return Y4GPU_ERR_CUDA; }
+	ctx->d_nodes = nodes; ctx->d_tris = tris;
+	Y4_CUDA(ctx, items_a.alloc(2ull * n + 2)); Y4_CUDA(ctx, items_b.alloc(2ull * n + 2));
+	const uint32_t init_counters[4] = {1u, 0u, 0u, 0u};   // node_counter, tri_counter, next_count, pad
+	Y4_CUDA(ctx, cudaMemcpyAsync(counters.p, init_counters, sizeof(init_counters), cudaMemcpyHostToDevice, st));
+	const uint32_t root_item[2] = {0u, 0u};
+	Y4_CUDA(ctx, cudaMemcpyAsync(items_a.p, root_item, sizeof(root_item), cudaMemcpyHostToDevice, st));
+	Y4BinTree bt;
+	bt.n = n; bt.left = left.p; bt.right = right.p; bt.first = first.p; bt.last = last.p; bt.box = box.p; bt.sorted_prim = sorted_prim;
+	uint32_t *cur = items_a.p, *nxt = items_b.p;
+	uint32_t count = 1;
+	int levels = 0;
+	while(count)
+	{
+		Y4CollapseOut out;
+		out.nodes = nodes; out.tris = tris; out.node_counter = counters.p; out.tri_counter = counters.p + 1;
+		out.next_items = nxt; out.next_count = counters.p + 2;
+		Y4_CUDA(ctx, cudaMemsetAsync(counters.p + 2, 0, sizeof(uint32_t), st));
+		k_collapse<<<(count + 127) / 128, 128, 0, st>>>(bt, leaf_max, cur, count, ctx->d_verts, ctx->d_flags, out);
+		Y4_CUDA(ctx, cudaMemcpyAsync(&count, counters.p + 2, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		Y4_CUDA(ctx, cudaStreamSynchronize(st));
+		uint32_t *t = cur; cur = nxt; nxt = t;
+		ctx->stats.kernel_launches++;
+		if(++levels > 256) { ctx->err = "collapse did not terminate"; return Y4GPU_ERR_CUDA; }
+	}
+	uint32_t fin[2];
+	Y4_CUDA(ctx, cudaMemcpyAsync(fin, counters.p, sizeof(fin), cudaMemcpyDeviceToHost, st));
+	Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	Y4_CUDA(ctx, cudaGetLastError());
+	if(fin[1] != (uint32_t) n) { ctx->err = "collapse lost triangles"; return Y4GPU_ERR_CUDA; }
+	ctx->n_nodes = fin[0];
+	// shrink the node array to its final size so only the live BVH stays resident
+	if(ctx->n_nodes < max_nodes)
+	{
+		Y4U4 *small = nullptr;
+		if(cudaMalloc(&small, ctx->n_nodes * Y4_NODE_WORDS * sizeof(Y4U4)) == cudaSuccess)
+		{
+			Y4_CUDA(ctx, cudaMemcpyAsync(small, nodes, ctx->n_nodes * Y4_NODE_WORDS * sizeof(Y4U4), cudaMemcpyDeviceToDevice, st));
+			Y4_CUDA(ctx, cudaStreamSynchronize(st));
+			cudaFree(nodes);
+			ctx->d_nodes = small;
+		}
+		else cudaGetLastError();
+	}
+	float ms = 0.f;
+	cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+	ctx->stats.build_ms = ms;
+	ctx->stats.n_tris = n; ctx->stats.n_nodes = ctx->n_nodes;
+	ctx->stats.node_bytes = ctx->n_nodes * Y4_NODE_WORDS * sizeof(Y4U4);
+	ctx->stats.tri_bytes = (uint64_t) n * sizeof(Y4Tri);
+	ctx->stats.kernel_launches += 5;
+	ctx->built = true;
+	return Y4GPU_OK;
+}

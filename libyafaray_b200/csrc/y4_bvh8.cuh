@@ -20,7 +20,7 @@
 #include "y4_tri.cuh"
 #include "y4_bvh_build.cuh"
 
-struct Y4U4 { uint32_t x, y, z, w; };   // one 128-bit node word (uint4 on device)
+struct alignas(16) Y4U4 { uint32_t x, y, z, w; };   // one 128-bit node word (uint4 on device)
 #define Y4_NODE_WORDS 5
 
 #if defined(__CUDA_ARCH__)

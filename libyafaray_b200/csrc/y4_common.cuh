@@ -62,8 +62,8 @@ Y4_HD V3 xscale(V3 a, float s) { return v3(xmul(s, a.x), xmul(s, a.y), xmul(s, a
 Y4_HD float xlen(V3 a) { return xsqrt(xdot(a, a)); }
 
 // ---- C-ABI mirrored PODs (include/y4gpu.h) ---------------------------------------------
-struct Y4Ray { float ox, oy, oz, tmin, dx, dy, dz, tmax; };   // 32 B, two float4 loads
-struct Y4Hit { float t, bu, bv; int32_t prim; };               // 16 B, one float4 store
+struct alignas(16) Y4Ray { float ox, oy, oz, tmin, dx, dy, dz, tmax; };   // 32 B, two float4 loads
+struct alignas(16) Y4Hit { float t, bu, bv; int32_t prim; };               // 16 B, one float4 store
 
 // Per-triangle visibility/material word.
 enum : uint32_t
@@ -81,7 +81,7 @@ enum { Y4_TRACE_CLOSEST = 0, Y4_TRACE_SHADOW = 1, Y4_TRACE_TSHADOW = 2 };
 // Device triangle record, 48 B = three 128-bit loads, stored in BVH leaf order.
 // e1/e2/eps are the reference's per-test temporaries (primitive_triangle.cc:47-49)
 // hoisted to build time; they are fp32-deterministic so the bits are unchanged.
-struct Y4Tri
+struct alignas(16) Y4Tri
 {
 	float v0x, v0y, v0z, eps;
 	float e1x, e1y, e1z; uint32_t prim;

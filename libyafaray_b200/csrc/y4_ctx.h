@@ -1,0 +1,62 @@
+// Context object behind the C-ABI (include/y4gpu.h).  Host-side only.
+#pragma once
+#include <cuda_runtime.h>
+#include <mutex>
+#include <string>
+#include "y4_trace.cuh"
+#include "../../include/y4gpu.h"
+
+struct Y4Pt;   // wavefront path tracer state (y4_pt.cu)
+
+struct y4gpu_ctx
+{
+	int device = 0;
+	int sm_count = 148;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	mutable std::mutex mtx;
+	std::string err;
+
+	// uploaded geometry (primitive order)
+	float *d_verts = nullptr;
+	uint32_t *d_flags = nullptr;
+	uint64_t n_tri = 0;
+
+	// accelerator
+	Y4U4 *d_nodes = nullptr;
+	Y4Tri *d_tris = nullptr;
+	uint64_t n_nodes = 0;
+	bool built = false;
+	float raw_bound[6] = {0, 0, 0, 0, 0, 0};
+	float bound[6] = {0, 0, 0, 0, 0, 0};
+
+	// staging for host-pointer batches and work counters
+	Y4Ray *d_rays = nullptr;
+	void *d_hits = nullptr;
+	uint64_t stage_cap = 0, stage_hit_bytes = 0;
+	uint32_t *d_work_counter = nullptr;
+	unsigned long long *d_visit_counters = nullptr;   // [2] nodes, tris
+	float *d_mat_transp = nullptr;
+	uint32_t mat_transp_cap = 0;
+
+	y4gpu_stats stats = {};
+	Y4Pt *pt = nullptr;
+
+	Y4Bvh8 view() const { Y4Bvh8 v; v.nodes = d_nodes; v.tris = d_tris; v.n_tris = (uint32_t) n_tri; return v; }
+};
+
+#define Y4_CUDA(ctx, call)                                                                       \
+	do {                                                                                         \
+		const cudaError_t e_ = (call);                                                           \
+		if(e_ != cudaSuccess)                                                                    \
+		{                                                                                        \
+			(ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                     \
+			return Y4GPU_ERR_CUDA;                                                               \
+		}                                                                                        \
+	} while(0)
+
+// y4_build.cu
+int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max);
+// y4_trace.cu
+int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out);
+int y4_launch_tshadow(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out);

@@ -72,6 +72,29 @@ Y4_HD float y4_safe_rcp(float d)
 	const float a = fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d);
 	return 1.f / a;
 }
+// 128-bit read-only loads of node words and triangle records
+Y4_HD Y4U4 y4_ld_u4(const Y4U4 *p)
+{
+#if defined(__CUDA_ARCH__)
+	const uint4 v = __ldg(reinterpret_cast<const uint4 *>(p));
+	Y4U4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w; return r;
+#else
+	return *p;
+#endif
+}
+Y4_HD Y4Tri y4_ld_tri(const Y4Tri *p)
+{
+#if defined(__CUDA_ARCH__)
+	const float4 a = __ldg(reinterpret_cast<const float4 *>(p)), b = __ldg(reinterpret_cast<const float4 *>(p) + 1), c = __ldg(reinterpret_cast<const float4 *>(p) + 2);
+	Y4Tri t;
+	t.v0x = a.x; t.v0y = a.y; t.v0z = a.z; t.eps = a.w;
+	t.e1x = b.x; t.e1y = b.y; t.e1z = b.z; t.prim = __float_as_uint(b.w);
+	t.e2x = c.x; t.e2y = c.y; t.e2z = c.z; t.flags = __float_as_uint(c.w);
+	return t;
+#else
+	return *p;
+#endif
+}
 Y4_HD uint32_t y4_byte(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
 
 // Intersect one node's 8 quantised child boxes; returns the hit mask in "priority" bit
@@ -125,7 +148,7 @@ Y4_HD uint32_t y4_node_hits(const Y4U4 w0, const Y4U4 w1, const Y4U4 w2, const Y
 // recorded in `filt` (distinct primitives) up to max_depth, see y4_kernels.cu for the colour.
 template<int KIND>
 Y4_HD void y4_trace_ray(const Y4Bvh8 &bvh, const Y4PreparedRay &ray, Y4Hit &hit, uint2 *stack,
-                        Y4TraceStats *stats, uint32_t *filt, int *n_filt, int max_depth)
+                        Y4TraceStats *stats, uint32_t *filt, uint32_t *filt_mat, int *n_filt, int max_depth)
 {
 	hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
 	if(bvh.n_tris == 0) return;
@@ -148,7 +171,7 @@ Y4_HD void y4_trace_ray(const Y4Bvh8 &bvh, const Y4PreparedRay &ray, Y4Hit &hit,
 			const uint32_t child = ngroup.x + y4_popc(ngroup.y & 0xffu & ((1u << slot) - 1u));
 			if(ngroup.y & 0xff000000u) stack[sp++] = ngroup;        // siblings still pending
 			const Y4U4 *n = bvh.nodes + (size_t) child * Y4_NODE_WORDS;
-			const Y4U4 w0 = n[0], w1 = n[1], w2 = n[2], w3 = n[3], w4 = n[4];
+			const Y4U4 w0 = y4_ld_u4(n), w1 = y4_ld_u4(n + 1), w2 = y4_ld_u4(n + 2), w3 = y4_ld_u4(n + 3), w4 = y4_ld_u4(n + 4);
 			if(stats) stats->nodes++;
 			const uint32_t hits = y4_node_hits(w0, w1, w2, w3, w4, ray.o, idir, oct_inv, ray.t_lo, t_hi);
 			ngroup.x = w1.x; ngroup.y = (hits & 0xff000000u) | (w0.w >> 24);
@@ -163,7 +186,7 @@ Y4_HD void y4_trace_ray(const Y4Bvh8 &bvh, const Y4PreparedRay &ray, Y4Hit &hit,
 		{
 			const uint32_t bit = y4_msb(tgroup.y);
 			tgroup.y &= ~(1u << bit);
-			const Y4Tri tr = bvh.tris[tgroup.x + bit];
+			const Y4Tri tr = y4_ld_tri(bvh.tris + tgroup.x + bit);
 			if(stats) stats->tris++;
 			float t, u, v;
 			if(!y4_tri_intersect(ray.o, ray.d, v3(tr.v0x, tr.v0y, tr.v0z), v3(tr.e1x, tr.e1y, tr.e1z), v3(tr.e2x, tr.e2y, tr.e2z), tr.eps, t, u, v)) continue;
@@ -190,7 +213,7 @@ Y4_HD void y4_trace_ray(const Y4Bvh8 &bvh, const Y4PreparedRay &ray, Y4Hit &hit,
 				if(!seen)
 				{
 					if(*n_filt >= max_depth) { hit.t = t; hit.bu = u; hit.bv = v; hit.prim = (int32_t) tr.prim; return; }
-					filt[(*n_filt)++] = tr.prim;
+					filt[*n_filt] = tr.prim; filt_mat[(*n_filt)++] = tr.flags >> Y4_TRI_MAT_SHIFT;
 				}
 			}
 		}

@@ -82,11 +82,11 @@ int emu_build_trace(const float *verts, const uint32_t *flags, int n, const floa
 		Y4Ray r; memcpy(&r, rays + 8ull * i, sizeof(r));
 		const Y4PreparedRay pr = y4_prepare_ray(r, kind);
 		uint2 stack[Y4_STACK_SIZE];
-		uint32_t filt[16]; int n_filt = 0;
+		uint32_t filt[16], filt_mat[16]; int n_filt = 0;
 		Y4TraceStats s{0, 0};
-		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray<Y4_TRACE_CLOSEST>(bvh, pr, hits[i], stack, &s, filt, &n_filt, 0);
-		else if(kind == Y4_TRACE_SHADOW) y4_trace_ray<Y4_TRACE_SHADOW>(bvh, pr, hits[i], stack, &s, filt, &n_filt, 0);
-		else y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, hits[i], stack, &s, filt, &n_filt, 8);
+		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray<Y4_TRACE_CLOSEST>(bvh, pr, hits[i], stack, &s, filt, filt_mat, &n_filt, 0);
+		else if(kind == Y4_TRACE_SHADOW) y4_trace_ray<Y4_TRACE_SHADOW>(bvh, pr, hits[i], stack, &s, filt, filt_mat, &n_filt, 0);
+		else y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, hits[i], stack, &s, filt, filt_mat, &n_filt, 8);
 		sn += s.nodes; st += s.tris;
 	}
 	if(stats_out) { stats_out[0] = sn; stats_out[1] = st; }

@@ -1,0 +1,83 @@
+"""Test helpers: run the reference oracle binaries (oracle/_ref, built from /root/reference by
+oracle/Makefile; shipped to the GPU box as built files) and the unit-test emulation."""
+import ctypes
+import json
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+HIT_DTYPE = np.dtype([("t", "f4"), ("bu", "f4"), ("bv", "f4"), ("prim", "i4")])
+
+
+def have_ref(name="ref_raybatch"):
+    return os.path.exists(os.path.join(REF_DIR, name))
+
+
+def ref_raybatch(tris, rays, kind, threads=0, accel="yafaray-kdtree-original"):
+    """Run the UNMODIFIED reference kd-tree on a ray batch -> (hits, info json)."""
+    with tempfile.TemporaryDirectory() as d:
+        tp, rp, hp = (os.path.join(d, n) for n in ("t.f32", "r.f32", "h.bin"))
+        np.ascontiguousarray(tris, np.float32).tofile(tp)
+        np.ascontiguousarray(rays, np.float32).tofile(rp)
+        cmd = [os.path.join(REF_DIR, "ref_raybatch"), tp, rp, kind, hp]
+        if threads:
+            cmd += [str(threads), accel]
+        out = subprocess.run(cmd, capture_output=True, text=True, check=True)
+        return np.fromfile(hp, HIT_DTYPE), json.loads(out.stdout.strip().splitlines()[-1])
+
+
+_emu = None
+
+
+def emu():
+    global _emu
+    if _emu is None:
+        d = os.path.join(ROOT, "tests", "emu")
+        so = os.path.join(d, "libemu.so")
+        subprocess.run(["make", "-s", "-C", d], check=True)
+        _emu = ctypes.CDLL(so)
+    return _emu
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+def emu_build_trace(tris, rays, kind, leaf_max=1, flags=None):
+    tris = np.ascontiguousarray(tris, np.float32)
+    rays = np.ascontiguousarray(rays, np.float32)
+    hits = np.zeros(len(rays), HIT_DTYPE)
+    stats = np.zeros(2, np.uint64)
+    n_nodes = emu().emu_build_trace(_p(tris), _p(flags), len(tris), _p(rays), len(rays), kind, leaf_max, _p(hits), _p(stats))
+    return hits, n_nodes, stats
+
+
+def emu_brute(tris, rays, kind, flags=None):
+    tris = np.ascontiguousarray(tris, np.float32)
+    rays = np.ascontiguousarray(rays, np.float32)
+    hits = np.zeros(len(rays), HIT_DTYPE)
+    emu().emu_brute(_p(tris), _p(flags), len(tris), _p(rays), len(rays), kind, _p(hits))
+    return hits
+
+
+def compare_closest(got, ref, rel=1e-5):
+    """Parity rule of BASELINE.json: identical prim except documented near-ties (|dt| <= rel*t);
+    t and barycentrics within rel where the prim agrees.  Returns a dict of counts."""
+    same = got["prim"] == ref["prim"]
+    both = (got["prim"] >= 0) & (ref["prim"] >= 0)
+    dt = np.abs(got["t"].astype(np.float64) - ref["t"].astype(np.float64))
+    near_tie = ~same & both & (dt <= rel * np.abs(ref["t"]))
+    bad = ~same & ~near_tie
+    ok = same & both
+    tol_t = dt[ok] <= rel * np.abs(ref["t"][ok])
+    tol_u = np.abs(got["bu"][ok] - ref["bu"][ok]) <= rel
+    tol_v = np.abs(got["bv"][ok] - ref["bv"][ok]) <= rel
+    return {
+        "n": len(got), "same": int(same.sum()), "near_tie": int(near_tie.sum()), "bad": int(bad.sum()),
+        "t_out_of_tol": int((~tol_t).sum()), "uv_out_of_tol": int((~tol_u).sum() + (~tol_v).sum()),
+        "bit_exact_t": int((got["t"][ok] == ref["t"][ok]).sum()), "n_hit_both": int(ok.sum()),
+    }
