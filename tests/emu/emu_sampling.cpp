@@ -1,0 +1,33 @@
+// UNIT-TEST EMULATION ONLY: host build of the Y4_HD sampling/maths restatement
+// (libyafaray_b200/csrc/y4_pt_sampling.cuh) so it can be checked against reference KATs.
+#include "../../libyafaray_b200/csrc/y4_pt_sampling.cuh"
+#include "../../libyafaray_b200/csrc/y4_faure.h"
+
+static Y4FaureHost g_faure = y4_faure_build();
+static Y4LdsTables tables()
+{
+	Y4LdsTables t; t.sigma = g_faure.sigma.data(); t.offset = g_faure.offset; t.prime = g_faure.prime; t.inv_prime = g_faure.inv_prime;
+	return t;
+}
+
+extern "C" {
+double emu_lds(int dim, uint32_t n) { return y4_lds(tables(), dim, n); }
+void emu_ri(uint32_t i, uint32_t r, float *out3, uint32_t *fnv)
+{
+	out3[0] = y4_ri_vdc(i, r); out3[1] = y4_ri_s(i, r); out3[2] = y4_ri_lp(i, r); *fnv = y4_fnv32a(i);
+}
+void emu_halton(uint32_t base, uint32_t start, int count, float *out)
+{
+	Y4Halton h = y4_halton_start(base, start);
+	for(int k = 0; k < count; ++k) out[k] = y4_halton_next(h);
+}
+void emu_trig(float x, float *out3) { out3[0] = y4_fast_sin(x); out3[1] = y4_fast_cos(x); out3[2] = y4_fast_exp(x * 0.5f); }
+void emu_coshemi(const float *n, float s1, float s2, float *out9)
+{
+	V3 u, v;
+	const V3 nn = v3(n[0], n[1], n[2]);
+	y4_coords_system(nn, u, v);
+	const V3 d = y4_cos_hemisphere(nn, u, v, s1, s2);
+	out9[0] = u.x; out9[1] = u.y; out9[2] = u.z; out9[3] = v.x; out9[4] = v.y; out9[5] = v.z; out9[6] = d.x; out9[7] = d.y; out9[8] = d.z;
+}
+}
