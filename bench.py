@@ -1,0 +1,461 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 ray/path back end (driver contract: see README/DESIGN.md).
+
+Workload (BASELINE.json configs[2], "C3"): the 1M-triangle procedurally displaced sphere and, per
+GPU and per step, one batch each of 16 Mi coherent primary closest-hit rays, 16 Mi any-hit shadow
+rays and 16 Mi incoherent cosine-diffuse closest-hit rays, traced through the C-ABI
+(include/y4gpu.h) by the hand-written sm_100a BVH8 kernels.  metric = Mrays/s, whole job.
+
+  python bench.py [--gpus N --steps K --warmup W]          our arm (torchrun for N > 1)
+  python bench.py --impl reference [...]                    the reference's CPU kd-tree, host cores
+
+Only the CPU legs (cpu_baseline, --impl reference) touch oracle/ (the compiled, unmodified
+reference); the measured GPU path never does and fails loudly without liby4gpu.so + a GPU.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (closest-hit primary + any-hit shadow + cosine-diffuse closest-hit, 1M-triangle displaced sphere)"
+UNIT = "Mrays/s"
+BATCHES = ("primary", "shadow", "diffuse")
+LIGHT = (2.0, 3.0, 4.0)
+SHADOW_BIAS, MIN_RAYDIST = 5.0e-4, 5.0e-5
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--res", type=int, default=4096, help="primary grid is res x res rays (16 Mi at 4096)")
+    ap.add_argument("--nu", type=int, default=1000, help="sphere longitude segments (nu * nu/2 * 2 triangles)")
+    ap.add_argument("--cpu-sample-res", type=int, default=512, help="CPU legs trace a (res/k)^2 strided subsample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def config_dict(args):
+    n = args.res * args.res
+    return {
+        "workload": "C3 (BASELINE configs[2]): 1M-triangle displaced sphere; per GPU per step 3 ray batches "
+                    "(coherent primary closest-hit, any-hit shadow, incoherent cosine-diffuse closest-hit)",
+        "n_tri": args.nu * (args.nu // 2) * 2,
+        "rays_per_batch": n,
+        "rays_per_step_per_gpu": 3 * n,
+        "l2": "no flush needed: each batch streams %d MiB of rays in and %d MiB of hits out (> 126 MB L2)" % (n * 32 >> 20, n * 16 >> 20),
+        "sharding": "independent ray batches per GPU (scene + BVH replicated), no data-path collective",
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi in the background during the timed regions)
+class ClockSampler:
+    Q = "timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.rows, self.marks = [], []
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.p = None
+            return
+        self.t = threading.Thread(target=self._read, daemon=True)
+        self.t.start()
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def mark(self, t0: float, t1: float):
+        self.marks.append((t0, t1))
+
+    def finish(self) -> dict:
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        inside = [r for (t, r) in self.rows if any(a - 0.05 <= t <= b + 0.15 for a, b in self.marks)]
+        scope = "timed regions"
+        if len(inside) < 3:
+            inside, scope = [r for _, r in self.rows], "whole run (timed regions shorter than the sampling period)"
+        sm, mx, pw, reasons = [], [], [], set()
+        for r in inside:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "scope": scope, "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic ray batches, generated on the device with torch (set-up plumbing, never timed)
+def camera_basis(rank: int):
+    """Pinhole at distance 3 from the sphere centre; rank r looks from a yaw of 45*r degrees."""
+    a = np.radians(45.0 * rank)
+    eye = np.array([3.0 * np.sin(a), 0.0, 3.0 * np.cos(a)])
+    fwd = -eye / np.linalg.norm(eye)
+    right = np.cross(fwd, [0.0, 1.0, 0.0])
+    right /= np.linalg.norm(right)
+    up = np.cross(right, fwd)
+    return eye, fwd, right, up
+
+
+def gen_primary(torch, res: int, rank: int, device, stride: int = 1):
+    eye, fwd, right, up = camera_basis(rank)
+    half = np.tan(np.radians(43.6) * 0.5)
+    idx = torch.arange(0, res, stride, device=device, dtype=torch.float64) + 0.5 * stride
+    x = (idx / res * 2 - 1) * half
+    y = (1 - idx / res * 2) * half
+    f, r, u = (torch.tensor(v, device=device, dtype=torch.float64) for v in (fwd, right, up))
+    d = f[None, None, :] + x[None, :, None] * r + y[:, None, None] * u
+    d = d / d.norm(dim=-1, keepdim=True)
+    n = d.shape[0] * d.shape[1]
+    rays = torch.empty((n, 8), device=device, dtype=torch.float32)
+    rays[:, 0:3] = torch.tensor(eye, device=device, dtype=torch.float32)
+    rays[:, 3] = 0.0
+    rays[:, 4:7] = d.reshape(-1, 3).float()
+    rays[:, 7] = -1.0
+    return rays
+
+
+def gen_secondary(torch, tris_d, rays, hits, seed: int):
+    """Shadow rays toward LIGHT and cosine-diffuse rays from the primary hit points (misses are
+    recycled from the hit list), reference bias conventions (integrator_montecarlo.cc:105-114,
+    integrator_path_tracer.cc:189)."""
+    n = rays.shape[0]
+    prim = hits[:, 3].view(torch.int32).long()
+    ok = prim >= 0
+    src_idx = torch.nonzero(ok).squeeze(1)
+    if src_idx.numel() == 0:
+        raise RuntimeError("no primary ray hit the scene")
+    pick = src_idx[torch.arange(n, device=rays.device) % src_idx.numel()]
+    o = rays[pick, 0:3].double() + rays[pick, 4:7].double() * hits[pick, 0:1].double()
+    tr = tris_d[prim[pick]].double().reshape(-1, 3, 3)
+    nn = torch.linalg.cross(tr[:, 1] - tr[:, 0], tr[:, 2] - tr[:, 0])
+    nn = nn / nn.norm(dim=-1, keepdim=True).clamp_min(1e-300)
+    flip = (nn * rays[pick, 4:7].double()).sum(-1) > 0
+    nn = torch.where(flip[:, None], -nn, nn)
+    del tr
+    # shadow
+    light = torch.tensor(LIGHT, device=rays.device, dtype=torch.float64)
+    d = light[None, :] - o
+    dist = d.norm(dim=-1)
+    sh = torch.empty((n, 8), device=rays.device, dtype=torch.float32)
+    sh[:, 0:3] = o.float()
+    sh[:, 3] = (SHADOW_BIAS * o.norm(dim=-1).clamp_min(1.0)).float()
+    sh[:, 4:7] = (d / dist[:, None]).float()
+    sh[:, 7] = dist.float()
+    del d, dist
+    # diffuse
+    g = torch.Generator(device=rays.device)
+    g.manual_seed(seed)
+    s1 = torch.rand(n, device=rays.device, dtype=torch.float64, generator=g)
+    s2 = torch.rand(n, device=rays.device, dtype=torch.float64, generator=g)
+    ax = torch.where(nn[:, 0:1].abs() > 0.5, torch.tensor([[0.0, 1.0, 0.0]], device=rays.device, dtype=torch.float64),
+                     torch.tensor([[1.0, 0.0, 0.0]], device=rays.device, dtype=torch.float64))
+    tu = torch.linalg.cross(nn, ax)
+    tu = tu / tu.norm(dim=-1, keepdim=True)
+    tv = torch.linalg.cross(nn, tu)
+    dd = (tu * torch.cos(2 * np.pi * s2)[:, None] + tv * torch.sin(2 * np.pi * s2)[:, None]) * torch.sqrt(1 - s1)[:, None] + nn * torch.sqrt(s1)[:, None]
+    dd = dd / dd.norm(dim=-1, keepdim=True)
+    df = torch.empty((n, 8), device=rays.device, dtype=torch.float32)
+    df[:, 0:3] = o.float()
+    df[:, 3] = MIN_RAYDIST
+    df[:, 4:7] = dd.float()
+    df[:, 7] = -1.0
+    return sh, df
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs: the UNMODIFIED reference kd-tree (oracle/_ref, built by oracle/Makefile) on the host cores
+def cpu_sample_batches_numpy(tris, res: int, server):
+    """All-CPU construction of the sample batches (used by --impl reference): primary grid, then
+    shadow / diffuse rays from the reference's own hits."""
+    from libyafaray_b200 import scenes
+
+    prim = scenes.primary_rays(res, res)
+    h, _ = server.trace(prim, "closest")
+    p, n, ok = scenes.hit_points_normals(tris, prim, h["t"], h["prim"])
+    return {"primary": prim, "shadow": scenes.shadow_rays(p, ok, LIGHT), "diffuse": scenes.diffuse_rays(p, n, ok)}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refserver
+    from libyafaray_b200 import scenes
+
+    line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(args)}
+    if not refserver.have_ref():
+        line["unavailable"] = "oracle/_ref/ref_raybatch is not built (run __graft_entry__.build() where /root/reference exists)"
+        print(json.dumps(line))
+        return
+    tris = scenes.displaced_sphere(args.nu, args.nu // 2)
+    with refserver.RefServer(tris, threads=0) as srv:
+        batches = cpu_sample_batches_numpy(tris, args.cpu_sample_res, srv)
+        kinds = {"primary": "closest", "shadow": "shadow", "diffuse": "closest"}
+        for _ in range(args.warmup):
+            for b in BATCHES:
+                srv.trace(batches[b], kinds[b])
+        per = {b: 0.0 for b in BATCHES}
+        for _ in range(args.steps):
+            for b in BATCHES:
+                per[b] += srv.trace(batches[b], kinds[b])[1]["trace_s"]
+        n = batches["primary"].shape[0]
+        total = sum(per.values())
+        value = 3 * n * args.steps / total * 1e-6
+        threads = srv.info["threads"]
+        line.update({
+            "value": value, "ms_per_step": total / args.steps * 1e3,
+            "breakdown_mrays_s": {b: n * args.steps / per[b] * 1e-6 for b in BATCHES},
+            "kd_build_s": srv.info["build_s"],
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "reference",
+                             "sample": "%dx%d primary grid + shadow + diffuse batches (%d rays each) per step; yafaray-kdtree-original, build (%.1f s, serial) not timed"
+                                       % (args.cpu_sample_res, args.cpu_sample_res, n, srv.info["build_s"])},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+        })
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md; MEASURED_PEAKS.json absent)"
+
+
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    from libyafaray_b200 import scenes
+    from libyafaray_b200.accelerator import AcceleratorB200
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- this back end has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    tris = scenes.displaced_sphere(args.nu, args.nu // 2)
+    acc = AcceleratorB200(tris, device=local)
+    stream = torch.cuda.Stream(device=dev)
+    acc.set_stream(stream.cuda_stream)
+    st0 = acc.stats()
+    tris_d = torch.from_numpy(tris).to(dev)
+    n = args.res * args.res
+    kinds = {"primary": acc.intersect, "shadow": acc.isShadowed, "diffuse": acc.intersect}
+
+    # ---- set-up: batches resident in HBM ---------------------------------------------------
+    rays = {"primary": gen_primary(torch, args.res, rank, dev)}
+    hits = {b: torch.empty((n, 4), device=dev, dtype=torch.float32) for b in BATCHES}
+    torch.cuda.synchronize()
+    acc.intersect(rays["primary"], hits["primary"])
+    acc.synchronize()
+    rays["shadow"], rays["diffuse"] = gen_secondary(torch, tris_d, rays["primary"], hits["primary"], seed=0xD1F + rank)
+    torch.cuda.synchronize()
+
+    # visit counters (deterministic per batch) -> algorithmic bytes per ray, SURVEY.md 8(d)
+    alg = {}
+    for b in BATCHES:
+        kinds[b](rays[b], hits[b], counted=True)
+        s = acc.stats()
+        npr, tpr = s["nodes_visited"] / n, s["tris_tested"] / n
+        out_b = 16 if b != "shadow" else 16   # the shadow kernel also writes the 16 B blocker record
+        alg[b] = {"nodes_per_ray": npr, "tris_per_ray": tpr, "bytes_per_ray": 32 + out_b + 80 * npr + 48 * tpr}
+
+    def step():
+        for b in BATCHES:
+            kinds[b](rays[b], hits[b])
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    # ---- timed region 1: device-resident throughput ------------------------------------------
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+    launches0 = acc.stats()["kernel_launches"]
+    barrier()
+    w0 = time.time()
+    for k in range(args.steps):
+        ev[k][0].record(stream)
+        for j, b in enumerate(BATCHES):
+            kinds[b](rays[b], hits[b])
+            ev[k][j + 1].record(stream)
+    stream.synchronize()
+    barrier()
+    w1 = time.time()
+    if sampler:
+        sampler.mark(w0, w1)
+    total_ms = ev[0][0].elapsed_time(ev[-1][3])
+    per_ms = {b: float(np.mean([ev[k][j].elapsed_time(ev[k][j + 1]) for k in range(args.steps)])) for j, b in enumerate(BATCHES)}
+    launches = acc.stats()["kernel_launches"] - launches0
+    hit_frac = {b: float((hits[b][:, 3].contiguous().view(torch.int32) >= 0).float().mean()) for b in BATCHES}
+
+    # ---- timed region 2: end to end through the plug-in call with HOST buffers ------------------
+    e2e = None
+    if not args.no_e2e:
+        h_rays = {b: torch.empty((n, 8), dtype=torch.float32, pin_memory=True) for b in BATCHES}
+        h_hits = {b: torch.empty((n, 4), dtype=torch.float32, pin_memory=True) for b in BATCHES}
+        for b in BATCHES:
+            h_rays[b].copy_(rays[b])
+        torch.cuda.synchronize()
+        e_steps = max(1, min(args.steps, 10))
+        for _ in range(min(args.warmup, 2)):
+            for b in BATCHES:
+                kinds[b](h_rays[b], h_hits[b])
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w2 = time.time()
+        e0.record(stream)
+        for _ in range(e_steps):
+            for b in BATCHES:
+                kinds[b](h_rays[b], h_hits[b])   # H2D of the rays, kernel, D2H of the hit records, sync
+        e1.record(stream)
+        stream.synchronize()
+        barrier()
+        w3 = time.time()
+        if sampler:
+            sampler.mark(w2, w3)
+        e2e_ms = e0.elapsed_time(e1)
+        same = all(bool(torch.equal(h_hits[b], hits[b].cpu())) for b in BATCHES)
+        e2e = {"ms": e2e_ms, "steps": e_steps, "identical_to_resident_run": same}
+
+    # ---- max over ranks ------------------------------------------------------------------------
+    t = torch.tensor([total_ms, e2e["ms"] if e2e else 0.0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(t[0]), float(t[1])
+
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        dom = max(BATCHES, key=lambda b: per_ms[b])
+        achieved = alg[dom]["bytes_per_ray"] * n / (per_ms[dom] * 1e-3) * 1e-9
+        value = 3.0 * n * world * args.steps / (total_ms * 1e-3) * 1e-6
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config_dict(args),
+            "breakdown_mrays_s": {b: n / per_ms[b] * 1e-3 for b in BATCHES},
+            "hit_fraction": hit_frac,
+            "bvh": {k: acc.stats()[k] for k in ("n_tris", "n_nodes", "node_bytes", "tri_bytes", "build_ms")},
+            "gpu_launches": int(launches),
+            "roofline": {
+                "bound": "hbm", "kernel": "k_trace<%s> (%s batch)" % ("SHADOW" if dom == "shadow" else "CLOSEST", dom),
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "launch_ms": per_ms[dom],
+                "algorithmic_bytes_per_ray": alg[dom]["bytes_per_ray"], "per_batch": alg,
+                "note": "algorithmic bytes = 32 B ray + 16 B hit + 80 B x BVH8 nodes visited + 48 B x triangles tested (SURVEY.md 8(d)); "
+                        "most node/triangle fetches are served by L2, DRAM traffic is far lower (see profiles/)",
+            },
+        }
+        if e2e:
+            line["e2e"] = {"value": 3.0 * n * world * e2e["steps"] / (e2e_ms * 1e-3) * 1e-6, "unit": UNIT,
+                           "h2d_bytes_per_step": 3 * n * 32, "d2h_bytes_per_step": 3 * n * 16, "steps": e2e["steps"],
+                           "identical_to_resident_run": e2e["identical_to_resident_run"],
+                           "api": "AcceleratorB200.intersect/isShadowed -> y4gpu_trace with pinned host ray/hit buffers"}
+        if sampler:
+            line["clocks"] = sampler.finish()
+        if world == 1 and not args.no_cpu_baseline:
+            line.update(cpu_baseline_leg(args, torch, acc, tris, tris_d, rays, hits, kinds))
+        print(json.dumps(line))
+        sys.stdout.flush()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def cpu_baseline_leg(args, torch, acc, tris, tris_d, rays, hits, kinds):
+    """cpu_baseline: the unmodified reference kd-tree on the host cores, on a strided subsample of
+    the very batches the GPU just traced; doubles as a full-size parity spot check."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refserver
+
+    if not refserver.have_ref():
+        return {"cpu_baseline": {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}}
+    stride = max(1, args.res // max(1, args.cpu_sample_res))
+    g = torch.arange(stride // 2, args.res, stride, device=tris_d.device)
+    idx = (g[:, None] * args.res + g[None, :]).reshape(-1)
+    m = int(idx.numel())
+    per, parity = {}, {}
+    with refserver.RefServer(tris, threads=0) as srv:
+        for b in BATCHES:
+            r = rays[b][idx].cpu().numpy()
+            got = hits[b][idx].cpu().numpy().view(refserver.HIT_DTYPE).reshape(-1)
+            ref, info = srv.trace(r, "shadow" if b == "shadow" else "closest", repeats=2)
+            per[b] = info["trace_s"]
+            if b == "shadow":
+                parity[b] = {"n": m, "occlusion_mismatch": int(((got["prim"] >= 0) != (ref["prim"] != -1)).sum())}
+            else:
+                same = got["prim"] == ref["prim"]
+                both = (got["prim"] >= 0) & (ref["prim"] >= 0)
+                dt = np.abs(got["t"].astype(np.float64) - ref["t"].astype(np.float64))
+                near = ~same & both & (dt <= 1e-5 * np.abs(ref["t"]))
+                ok = same & both
+                parity[b] = {"n": m, "same_prim": int(same.sum()), "near_tie": int(near.sum()), "bad": int((~same & ~near).sum()),
+                             "t_bit_exact": int((got["t"][ok] == ref["t"][ok]).sum()), "n_hit_both": int(ok.sum()),
+                             "uv_bit_exact": int(((got["bu"][ok] == ref["bu"][ok]) & (got["bv"][ok] == ref["bv"][ok])).sum())}
+        threads, build_s = srv.info["threads"], srv.info["build_s"]
+    total = sum(per.values())
+    return {
+        "cpu_baseline": {"value": 3 * m / total * 1e-6, "unit": UNIT, "cores": threads, "kind": "reference",
+                         "breakdown_mrays_s": {b: m / per[b] * 1e-6 for b in BATCHES}, "kd_build_s": build_s,
+                         "sample": "every %dth ray in x and y of each 16 Mi batch (%d rays per batch, mean of 2 repeats); "
+                                   "yafaray-kdtree-original from oracle/_ref on all host threads, serial kd build not timed" % (stride, m)},
+        "parity_sample_vs_reference": parity,
+    }
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -86,6 +86,11 @@ void y4gpu_destroy(y4gpu_ctx *ctx);
 const char *y4gpu_last_error(const y4gpu_ctx *ctx);   /* ctx may be NULL: last create error */
 int y4gpu_device_count(void);
 
+/* Run all work of this ctx on the caller's CUDA stream (cudaStream_t passed as void*; NULL
+ * restores the ctx's own non-blocking stream).  Lets a host application order the ctx's
+ * kernels against its own copies/kernels without extra synchronisation. */
+int y4gpu_set_stream(y4gpu_ctx *ctx, void *cuda_stream);
+
 /* pinned host buffers for callers that want async copies (optional) */
 void *y4gpu_host_alloc(uint64_t bytes);
 void y4gpu_host_free(void *p);

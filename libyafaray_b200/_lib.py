@@ -46,7 +46,7 @@ _lib = None
 # every symbol include/y4gpu.h declares (checked by tests/test_cabi.py)
 EXPORTED = [
     "y4gpu_create", "y4gpu_destroy", "y4gpu_last_error", "y4gpu_device_count",
-    "y4gpu_host_alloc", "y4gpu_host_free",
+    "y4gpu_set_stream", "y4gpu_host_alloc", "y4gpu_host_free",
     "y4gpu_upload_triangles", "y4gpu_build", "y4gpu_get_bound",
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow",
     "y4gpu_get_stats", "y4gpu_synchronize",
@@ -70,6 +70,8 @@ def lib() -> C.CDLL:
     L.y4gpu_last_error.restype = C.c_char_p
     L.y4gpu_device_count.argtypes = []
     L.y4gpu_device_count.restype = i32
+    L.y4gpu_set_stream.argtypes = [vp, vp]
+    L.y4gpu_set_stream.restype = i32
     L.y4gpu_host_alloc.argtypes = [u64]
     L.y4gpu_host_alloc.restype = vp
     L.y4gpu_host_free.argtypes = [vp]

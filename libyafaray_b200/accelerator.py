@@ -127,6 +127,10 @@ class AcceleratorB200:
 
     intersectTs = isShadowedTransparent
 
+    def set_stream(self, cuda_stream: int) -> None:
+        """Run this accelerator's kernels/copies on the caller's CUDA stream (0/None = its own)."""
+        _lib.check(self._ctx, self._L.y4gpu_set_stream(self._ctx, C.c_void_p(int(cuda_stream or 0))), "y4gpu_set_stream")
+
     # -- diagnostics -------------------------------------------------------------------------
     def synchronize(self) -> None:
         _lib.check(self._ctx, self._L.y4gpu_synchronize(self._ctx), "y4gpu_synchronize")

@@ -39,10 +39,11 @@ int y4gpu_create(int device, y4gpu_ctx **out)
 	ctx->device = device;
 	cudaDeviceProp prop;
 	if(cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
-	bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess
+	bool ok = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess
 		&& cudaEventCreate(&ctx->ev0) == cudaSuccess && cudaEventCreate(&ctx->ev1) == cudaSuccess
 		&& cudaMalloc(&ctx->d_work_counter, 64) == cudaSuccess
 		&& cudaMalloc(&ctx->d_visit_counters, 64) == cudaSuccess;
+	ctx->stream = ctx->own_stream;
 	if(!ok)
 	{
 		g_create_err = std::string("context setup failed: ") + cudaGetErrorString(cudaGetLastError());
@@ -66,7 +67,7 @@ void y4gpu_destroy(y4gpu_ctx *ctx)
 	cudaFree(ctx->d_mat_transp);
 	if(ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if(ctx->ev1) cudaEventDestroy(ctx->ev1);
-	if(ctx->stream) cudaStreamDestroy(ctx->stream);
+	if(ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 }
 
@@ -195,6 +196,16 @@ int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int m
 	if(rc) return rc;
 	if(!out_dev) Y4_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * sizeof(y4gpu_tshit), cudaMemcpyDeviceToHost, ctx->stream));
 	Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return Y4GPU_OK;
+}
+
+int y4gpu_set_stream(y4gpu_ctx *ctx, void *cuda_stream)
+{
+	if(!ctx) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	ctx->stream = cuda_stream ? (cudaStream_t) cuda_stream : ctx->own_stream;
 	return Y4GPU_OK;
 }
 

@@ -12,7 +12,8 @@ struct y4gpu_ctx
 {
 	int device = 0;
 	int sm_count = 148;
-	cudaStream_t stream = nullptr;
+	cudaStream_t stream = nullptr;      // stream in use (own_stream or the caller's)
+	cudaStream_t own_stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	mutable std::mutex mtx;
 	std::string err;

@@ -8,6 +8,9 @@
 //   Accelerator::isShadowed(ray, bias)       (src/accelerator/accelerator.cc:69-80 -> intersectS :775-904)
 //
 // usage: ref_raybatch <tris.f32> <rays.f32> <closest|shadow> <hits.out> [threads] [accel_type]
+//        ref_raybatch <tris.f32> --serve - - [threads] [accel_type]
+//          serve mode: builds the kd-tree once, prints one JSON line, then answers each stdin line
+//          "<closest|shadow> <rays.f32> <hits.out> [repeats]" with one JSON timing line (used by bench.py's CPU legs)
 //   tris.f32 : n_tri * 9 floats (v0 v1 v2, world space); triangle i == primitive index i
 //   rays.f32 : n_ray * 8 floats (ox oy oz tmin dx dy dz tmax); tmax < 0 means "no limit"
 //   hits.out : n_ray * {float t, float bu, float bv, int32 prim}; prim = -1 on miss.
@@ -51,12 +54,12 @@ int main(int argc, char **argv)
 {
 	if(argc < 5) { fprintf(stderr, "usage: %s tris rays closest|shadow out [threads] [accel]\n", argv[0]); return 2; }
 	const std::vector<float> tris = readFloats(argv[1]);
-	const std::vector<float> rays = readFloats(argv[2]);
-	const bool shadow = strcmp(argv[3], "shadow") == 0;
+	const bool serve = strcmp(argv[2], "--serve") == 0;
 	int n_threads = argc > 5 ? atoi(argv[5]) : (int) std::thread::hardware_concurrency();
+	if(n_threads < 1) n_threads = (int) std::thread::hardware_concurrency();
 	if(n_threads < 1) n_threads = 1;
 	const std::string accel_type = argc > 6 ? argv[6] : "yafaray-kdtree-original";
-	const size_t n_tri = tris.size() / 9, n_ray = rays.size() / 8;
+	const size_t n_tri = tris.size() / 9;
 
 	Logger logger(nullptr, nullptr, YAFARAY_DISPLAY_CONSOLE_HIDDEN);
 	logger.setConsoleMasterVerbosity(YAFARAY_LOG_LEVEL_MUTE);
@@ -87,57 +90,96 @@ int main(int argc, char **argv)
 	std::unique_ptr<const Accelerator> accel(Accelerator::factory(logger, prims, ap));
 	const auto t1 = std::chrono::steady_clock::now();
 	const Bound bound = accel->getBound();
-
-	std::vector<HitRec> out(n_ray);
-	auto worker = [&](int tid)
-	{
-		// block-cyclic over the batch so every thread sees similar coherence
-		const size_t block = 4096;
-		for(size_t b = (size_t) tid * block; b < n_ray; b += (size_t) n_threads * block)
-		{
-			const size_t e = std::min(n_ray, b + block);
-			for(size_t i = b; i < e; ++i)
-			{
-				const float *r = &rays[8 * i];
-				Ray ray({r[0], r[1], r[2]}, {r[4], r[5], r[6]}, r[3], r[7]);
-				HitRec h{0.f, 0.f, 0.f, -1};
-				if(shadow)
-				{
-					const auto res = accel->isShadowed(ray, 0.f);
-					if(res.first) h.prim = res.second ? index_of[res.second] : -2;
-				}
-				else
-				{
-					const float t_max = (ray.tmax_ >= 0.f) ? ray.tmax_ : std::numeric_limits<float>::infinity();
-					const AcceleratorIntersectData d = accel->intersect(ray, t_max);
-					if(d.hit_ && d.hit_primitive_)
-					{
-						h.t = d.t_hit_; h.bu = d.barycentric_v_; h.bv = d.barycentric_w_;
-						h.prim = index_of[d.hit_primitive_];
-					}
-				}
-				out[i] = h;
-			}
-		}
-	};
-	const auto t2 = std::chrono::steady_clock::now();
-	std::vector<std::thread> th;
-	for(int t = 0; t < n_threads; ++t) th.emplace_back(worker, t);
-	for(auto &t : th) t.join();
-	const auto t3 = std::chrono::steady_clock::now();
-
-	FILE *fo = fopen(argv[4], "wb");
-	if(!fo) { fprintf(stderr, "cannot write %s\n", argv[4]); return 2; }
-	fwrite(out.data(), sizeof(HitRec), out.size(), fo);
-	fclose(fo);
-	size_t n_hit = 0;
-	for(const auto &h : out) n_hit += h.prim != -1;
 	const double build_s = std::chrono::duration<double>(t1 - t0).count();
-	const double trace_s = std::chrono::duration<double>(t3 - t2).count();
-	printf("{\"impl\": \"reference\", \"accel\": \"%s\", \"kind\": \"%s\", \"n_tri\": %zu, \"n_ray\": %zu, \"n_hit\": %zu, "
-		   "\"threads\": %d, \"build_s\": %.6f, \"trace_s\": %.6f, \"mrays_per_s\": %.6f, "
-		   "\"bound\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g]}\n",
-		   accel_type.c_str(), shadow ? "shadow" : "closest", n_tri, n_ray, n_hit, n_threads, build_s, trace_s,
-		   n_ray / trace_s * 1e-6, bound.a_.x(), bound.a_.y(), bound.a_.z(), bound.g_.x(), bound.g_.y(), bound.g_.z());
+
+	// traces one batch with n_threads host threads; returns seconds
+	auto trace = [&](const std::vector<float> &rays, bool shadow, std::vector<HitRec> &out) -> double
+	{
+		const size_t n_ray = rays.size() / 8;
+		out.resize(n_ray);
+		auto worker = [&](int tid)
+		{
+			// block-cyclic over the batch so every thread sees similar coherence
+			const size_t block = 4096;
+			for(size_t b = (size_t) tid * block; b < n_ray; b += (size_t) n_threads * block)
+			{
+				const size_t e = std::min(n_ray, b + block);
+				for(size_t i = b; i < e; ++i)
+				{
+					const float *r = &rays[8 * i];
+					Ray ray({r[0], r[1], r[2]}, {r[4], r[5], r[6]}, r[3], r[7]);
+					HitRec h{0.f, 0.f, 0.f, -1};
+					if(shadow)
+					{
+						const auto res = accel->isShadowed(ray, 0.f);
+						if(res.first) h.prim = res.second ? index_of[res.second] : -2;
+					}
+					else
+					{
+						const float t_max = (ray.tmax_ >= 0.f) ? ray.tmax_ : std::numeric_limits<float>::infinity();
+						const AcceleratorIntersectData d = accel->intersect(ray, t_max);
+						if(d.hit_ && d.hit_primitive_)
+						{
+							h.t = d.t_hit_; h.bu = d.barycentric_v_; h.bv = d.barycentric_w_;
+							h.prim = index_of[d.hit_primitive_];
+						}
+					}
+					out[i] = h;
+				}
+			}
+		};
+		const auto t2 = std::chrono::steady_clock::now();
+		std::vector<std::thread> th;
+		for(int t = 0; t < n_threads; ++t) th.emplace_back(worker, t);
+		for(auto &t : th) t.join();
+		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t2).count();
+	};
+	auto writeHits = [](const char *path, const std::vector<HitRec> &out) -> bool
+	{
+		FILE *fo = fopen(path, "wb");
+		if(!fo) { fprintf(stderr, "cannot write %s\n", path); return false; }
+		fwrite(out.data(), sizeof(HitRec), out.size(), fo);
+		fclose(fo);
+		return true;
+	};
+	auto report = [&](const char *kind, size_t n_ray, const std::vector<HitRec> &out, double trace_s, int repeats)
+	{
+		size_t n_hit = 0;
+		for(const auto &h : out) n_hit += h.prim != -1;
+		printf("{\"impl\": \"reference\", \"accel\": \"%s\", \"kind\": \"%s\", \"n_tri\": %zu, \"n_ray\": %zu, \"n_hit\": %zu, "
+			   "\"threads\": %d, \"build_s\": %.6f, \"trace_s\": %.6f, \"repeats\": %d, \"mrays_per_s\": %.6f, "
+			   "\"bound\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g]}\n",
+			   accel_type.c_str(), kind, n_tri, n_ray, n_hit, n_threads, build_s, trace_s, repeats,
+			   trace_s > 0. ? n_ray / trace_s * 1e-6 : 0., bound.a_.x(), bound.a_.y(), bound.a_.z(), bound.g_.x(), bound.g_.y(), bound.g_.z());
+		fflush(stdout);
+	};
+
+	std::vector<HitRec> out;
+	if(!serve)
+	{
+		const std::vector<float> rays = readFloats(argv[2]);
+		const bool shadow = strcmp(argv[3], "shadow") == 0;
+		const double trace_s = trace(rays, shadow, out);
+		if(!writeHits(argv[4], out)) return 2;
+		report(shadow ? "shadow" : "closest", rays.size() / 8, out, trace_s, 1);
+		return 0;
+	}
+	report("build", 0, out, 0., 0);
+	char kind[32], rays_path[4096], out_path[4096];
+	char line[9000];
+	while(fgets(line, sizeof(line), stdin))
+	{
+		int repeats = 1;
+		const int got = sscanf(line, "%31s %4095s %4095s %d", kind, rays_path, out_path, &repeats);
+		if(got < 3) break;
+		if(repeats < 1) repeats = 1;
+		const std::vector<float> rays = readFloats(rays_path);
+		const bool shadow = strcmp(kind, "shadow") == 0;
+		double best = 1e30;   // serve mode reports the mean over repeats in trace_s
+		double sum = 0.;
+		for(int r = 0; r < repeats; ++r) { const double s = trace(rays, shadow, out); sum += s; if(s < best) best = s; }
+		if(!writeHits(out_path, out)) return 2;
+		report(shadow ? "shadow" : "closest", rays.size() / 8, out, sum / repeats, repeats);
+	}
 	return 0;
 }

@@ -4,6 +4,7 @@ import ctypes
 import json
 import os
 import subprocess
+import sys
 import tempfile
 
 import numpy as np
@@ -81,3 +82,7 @@ def compare_closest(got, ref, rel=1e-5):
         "t_out_of_tol": int((~tol_t).sum()), "uv_out_of_tol": int((~tol_u).sum() + (~tol_v).sum()),
         "bit_exact_t": int((got["t"][ok] == ref["t"][ok]).sum()), "n_hit_both": int(ok.sum()),
     }
+
+
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+from refserver import RefServer  # noqa: E402,F401
