@@ -361,7 +361,7 @@ def run_b200_arm(args):
         if sampler:
             sampler.mark(w2, w3)
         e2e_ms = e0.elapsed_time(e1)
-        same = all(bool(torch.equal(h_hits[b], hits[b].cpu())) for b in BATCHES)
+        same = all(bool(torch.equal(h_hits[b].view(torch.int32), hits[b].cpu().view(torch.int32))) for b in BATCHES)
         e2e = {"ms": e2e_ms, "steps": e_steps, "identical_to_resident_run": same}
 
     # ---- max over ranks ------------------------------------------------------------------------

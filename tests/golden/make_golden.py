@@ -1,0 +1,54 @@
+"""Regenerates the committed golden fixtures from the UNMODIFIED reference (oracle/_ref, built
+from /root/reference by `make -C oracle ref`).  Run in the build container only:
+
+    python tests/golden/make_golden.py
+
+  kat_sampling.json  <- oracle/_ref/ref_kat   (Halton/LDS/riVdC/riS/riLp/fnv, FAST_TRIG, cosHemisphere)
+  rays_sphere.npz    <- oracle/_ref/ref_raybatch on scenes.displaced_sphere(40, 20): primary,
+                        shadow and diffuse batches with the reference kd-tree's hit records
+  rays_soup.npz      <- same on scenes.triangle_soup(3000) with incoherent + segment rays
+"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import helpers  # noqa: E402
+from libyafaray_b200 import scenes  # noqa: E402
+
+
+def main():
+    out = subprocess.run([os.path.join(helpers.REF_DIR, "ref_kat")], capture_output=True, text=True, check=True).stdout
+    with open(os.path.join(HERE, "kat_sampling.json"), "w") as f:
+        f.write(out)
+
+    tris = scenes.displaced_sphere(40, 20)
+    prim = scenes.primary_rays(64, 64)
+    with helpers.RefServer(tris, threads=1) as srv:
+        h_prim, _ = srv.trace(prim, "closest")
+        p, n, ok = scenes.hit_points_normals(tris, prim, h_prim["t"], h_prim["prim"])
+        sh, df = scenes.shadow_rays(p, ok), scenes.diffuse_rays(p, n, ok)
+        h_sh, _ = srv.trace(sh, "shadow")
+        h_df, _ = srv.trace(df, "closest")
+        bound = np.array(srv.info["bound"], np.float32)
+    np.savez_compressed(os.path.join(HERE, "rays_sphere.npz"), scene=np.array([40, 20]), primary=prim, shadow=sh, diffuse=df,
+                        hit_primary=h_prim, hit_shadow=h_sh, hit_diffuse=h_df, bound=bound)
+
+    tris = scenes.triangle_soup(3000)
+    inc, seg = scenes.incoherent_rays(4096), scenes.segment_rays(4096)
+    with helpers.RefServer(tris, threads=1) as srv:
+        h_inc, _ = srv.trace(inc, "closest")
+        h_seg, _ = srv.trace(seg, "shadow")
+        bound = np.array(srv.info["bound"], np.float32)
+    np.savez_compressed(os.path.join(HERE, "rays_soup.npz"), scene=np.array([3000]), incoherent=inc, segment=seg,
+                        hit_incoherent=h_inc, hit_segment=h_seg, bound=bound)
+    print("golden fixtures written")
+
+
+if __name__ == "__main__":
+    main()
