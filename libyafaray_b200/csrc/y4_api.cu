@@ -2,6 +2,7 @@
 // No CPU fallback: every compute entry point returns Y4GPU_ERR_CUDA when CUDA is unusable.
 #include "y4_ctx.h"
 #include <cstring>
+#include <cstdlib>
 
 static std::string g_create_err;
 
@@ -42,7 +43,10 @@ int y4gpu_create(int device, y4gpu_ctx **out)
 	bool ok = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) == cudaSuccess
 		&& cudaEventCreate(&ctx->ev0) == cudaSuccess && cudaEventCreate(&ctx->ev1) == cudaSuccess
 		&& cudaMalloc(&ctx->d_work_counter, 64) == cudaSuccess
-		&& cudaMalloc(&ctx->d_visit_counters, 64) == cudaSuccess;
+		&& cudaMalloc(&ctx->d_visit_counters, 64) == cudaSuccess
+		&& cudaMalloc(&ctx->d_consts, 64) == cudaSuccess;
+	const uint32_t consts[4] = {0x4B000000u, 0u, 0u, 0u};
+	ok = ok && cudaMemcpy(ctx->d_consts, consts, sizeof(consts), cudaMemcpyHostToDevice) == cudaSuccess;
 	ctx->stream = ctx->own_stream;
 	if(!ok)
 	{
@@ -50,6 +54,9 @@ int y4gpu_create(int device, y4gpu_ctx **out)
 		delete ctx;
 		return Y4GPU_ERR_CUDA;
 	}
+	if(const char *e = getenv("Y4GPU_FETCH_THRESHOLD")) ctx->fetch_threshold = atoi(e);
+	if(const char *e = getenv("Y4GPU_POSTPONE_DIV")) ctx->postpone_div = atoi(e);
+	if(const char *e = getenv("Y4GPU_MIN_BLOCKS")) ctx->min_blocks = atoi(e);
 	*out = ctx;
 	return Y4GPU_OK;
 }
@@ -63,7 +70,7 @@ void y4gpu_destroy(y4gpu_ctx *ctx)
 	if(ctx->stream) cudaStreamSynchronize(ctx->stream);
 	y4gpu_pt_release(ctx);
 	cudaFree(ctx->d_verts); cudaFree(ctx->d_flags); cudaFree(ctx->d_nodes); cudaFree(ctx->d_tris);
-	cudaFree(ctx->d_rays); cudaFree(ctx->d_hits); cudaFree(ctx->d_work_counter); cudaFree(ctx->d_visit_counters);
+	cudaFree(ctx->d_rays); cudaFree(ctx->d_hits); cudaFree(ctx->d_work_counter); cudaFree(ctx->d_visit_counters); cudaFree(ctx->d_consts);
 	cudaFree(ctx->d_mat_transp);
 	if(ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if(ctx->ev1) cudaEventDestroy(ctx->ev1);

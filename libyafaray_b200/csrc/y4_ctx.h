@@ -36,14 +36,18 @@ struct y4gpu_ctx
 	void *d_hits = nullptr;
 	uint64_t stage_cap = 0, stage_hit_bytes = 0;
 	uint32_t *d_work_counter = nullptr;
+	uint32_t *d_consts = nullptr;                     // [0] = 0x4B000000, see y4_byte_m
 	unsigned long long *d_visit_counters = nullptr;   // [2] nodes, tris
 	float *d_mat_transp = nullptr;
 	uint32_t mat_transp_cap = 0;
 
+	// warp scheduling knobs of k_trace (env Y4GPU_FETCH_THRESHOLD / Y4GPU_POSTPONE_DIV override)
+	int fetch_threshold = 20, postpone_div = 5, min_blocks = 3;
+
 	y4gpu_stats stats = {};
 	Y4Pt *pt = nullptr;
 
-	Y4Bvh8 view() const { Y4Bvh8 v; v.nodes = d_nodes; v.tris = d_tris; v.n_tris = (uint32_t) n_tri; return v; }
+	Y4Bvh8 view() const { Y4Bvh8 v; v.nodes = d_nodes; v.tris = d_tris; v.n_tris = (uint32_t) n_tri; v.consts = d_consts; return v; }
 };
 
 #define Y4_CUDA(ctx, call)                                                                       \

@@ -11,34 +11,121 @@ namespace {
 
 constexpr int kTraceThreads = 256;
 
-template<int KIND, bool COUNT>
-__global__ void __launch_bounds__(kTraceThreads) k_trace(Y4Bvh8 bvh, const Y4Ray *__restrict__ rays, uint64_t n, Y4Hit *__restrict__ out,
-                                                         uint32_t *__restrict__ work_counter, unsigned long long *__restrict__ visit)
+// Warp-level scheduling around the per-ray logic of y4_trace.cuh:
+//  * dynamic ray fetch -- lanes whose ray has terminated are refilled from the global ray counter as
+//    soon as fewer than `fetch_threshold` lanes of the warp are still traversing (warp-level ray
+//    compaction: the warp never idles behind its longest ray);
+//  * postponed triangle tests -- when less than 1/postpone_div of the lanes that entered the
+//    triangle phase still have triangles pending, the rest of the triangle group goes onto the
+//    traversal stack so the warp returns to (convergent) node traversal;
+//  * shadow rays leave at the first accepted blocker (any-hit) and their lane is refilled.
+// Results do not depend on the schedule: closest hits use the order-independent rule y4_accept_t.
+template<int KIND, bool COUNT, int MINB>
+__global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const Y4Ray *__restrict__ rays, uint64_t n, Y4Hit *__restrict__ out,
+                                                         unsigned long long *__restrict__ work_counter, unsigned long long *__restrict__ visit,
+                                                         int fetch_threshold, int postpone_div)
 {
 	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t lt_mask = (1u << lane) - 1u;
+	const uint32_t vis_bit = KIND == Y4_TRACE_CLOSEST ? Y4_TRI_VIS_CLOSEST : Y4_TRI_VIS_SHADOW;
 	uint2 stack[Y4_STACK_SIZE];
 	unsigned long long my_nodes = 0, my_tris = 0;
-	const uint64_t n_packets = (n + 31u) >> 5;
+	bool have = false, exhausted = false;
+	uint64_t ray_i = 0;
+	Y4RayCtx rc = y4_ray_ctx(v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 1.f));
+	float t_lo = 0.f, t_hi = 0.f;
+	Y4Hit hit; hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
+	uint2 ngroup; ngroup.x = 0u; ngroup.y = 0u;
+	int sp = 0;
+	const uint32_t magic = __ldg(bvh.consts);
 	while(true)
 	{
-		uint32_t packet = 0;
-		if(lane == 0) packet = atomicAdd(work_counter, 1u);
-		packet = __shfl_sync(0xffffffffu, packet, 0);
-		if(packet >= n_packets) break;
-		const uint64_t i = ((uint64_t) packet << 5) + lane;
-		if(i < n)
+		// ---- refill idle lanes -------------------------------------------------------------
+		const uint32_t idle = __ballot_sync(0xffffffffu, !have);
+		if(idle && !exhausted)
 		{
-			const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + i));
-			const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + i) + 1);
-			Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
-			const Y4PreparedRay pr = y4_prepare_ray(r, KIND);
-			Y4Hit h;
-			Y4TraceStats s; s.nodes = 0; s.tris = 0;
-			y4_trace_ray<KIND>(bvh, pr, h, stack, COUNT ? &s : nullptr, nullptr, nullptr, nullptr, 0);
-			if(COUNT) { my_nodes += s.nodes; my_tris += s.tris; }
-			float4 o; o.x = h.t; o.y = h.bu; o.z = h.bv; o.w = __int_as_float(h.prim);
-			*reinterpret_cast<float4 *>(out + i) = o;
+			const uint32_t n_idle = __popc(idle);
+			unsigned long long base = 0;
+			if(lane == 0) base = atomicAdd(work_counter, (unsigned long long) n_idle);
+			base = __shfl_sync(0xffffffffu, base, 0);
+			exhausted = base + n_idle >= n;
+			const uint64_t mine = base + __popc(idle & lt_mask);
+			if(!have && mine < n)
+			{
+				const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + mine));
+				const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + mine) + 1);
+				Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
+				const Y4PreparedRay pr = y4_prepare_ray(r, KIND);
+				rc = y4_ray_ctx(pr.o, pr.d);
+				t_lo = pr.t_lo; t_hi = pr.t_hi;
+				hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
+				ray_i = mine; sp = 0; have = true;
+				// virtual parent of the root: child_base 0, imask = slot 0, hit bit at slot 0's priority
+				ngroup.x = 0u; ngroup.y = bvh.n_tris ? ((1u << (24u + rc.oct_inv)) | 1u) : 0u;
+			}
 		}
+		if(!__any_sync(0xffffffffu, have)) break;
+		const int leave_below = exhausted ? 0 : fetch_threshold;
+		// ---- traverse ----------------------------------------------------------------------
+		while(have)
+		{
+			uint2 tgroup; tgroup.x = 0u; tgroup.y = 0u;
+			if(ngroup.y & 0xff000000u)
+			{
+				const uint32_t bit = 31u - (uint32_t) __clz((int) ngroup.y);
+				ngroup.y &= ~(1u << bit);
+				const uint32_t slot = (bit - 24u) ^ rc.oct_inv;
+				const uint32_t child = ngroup.x + __popc(ngroup.y & 0xffu & ((1u << slot) - 1u));
+				if(ngroup.y & 0xff000000u) stack[sp++] = ngroup;        // siblings still pending
+				const Y4U4 *nd = bvh.nodes + (size_t) child * Y4_NODE_WORDS;
+				const Y4U4 w0 = y4_ld_u4(nd), w1 = y4_ld_u4(nd + 1), w2 = y4_ld_u4(nd + 2), w3 = y4_ld_u4(nd + 3), w4 = y4_ld_u4(nd + 4);
+				if(COUNT) my_nodes++;
+				const uint32_t hits = y4_node_hits(w0, w1, w2, w3, w4, rc.o, rc.idir, rc.oct_inv, t_lo, t_hi, magic);
+				ngroup.x = w1.x; ngroup.y = (hits & 0xff000000u) | (w0.w >> 24);
+				tgroup.x = w1.y; tgroup.y = hits & 0x00ffffffu;
+			}
+			else
+			{
+				tgroup = ngroup;            // a postponed triangle group came off the stack (or nothing)
+				ngroup.y = 0u;
+			}
+			// triangles of this group
+			const int entered = __popc(__activemask());
+			bool done = false;
+			while(tgroup.y)
+			{
+				if(postpone_div > 0 && sp < Y4_STACK_SIZE - 4 && __popc(__activemask()) * postpone_div < entered)
+				{
+					stack[sp++] = tgroup;
+					break;
+				}
+				const uint32_t bit = 31u - (uint32_t) __clz((int) tgroup.y);
+				tgroup.y &= ~(1u << bit);
+				const Y4Tri tr = y4_ld_tri(bvh.tris + tgroup.x + bit);
+				if(COUNT) my_tris++;
+				float t, u, v;
+				if(!y4_tri_intersect(rc.o, rc.d, v3(tr.v0x, tr.v0y, tr.v0z), v3(tr.e1x, tr.e1y, tr.e1z), v3(tr.e2x, tr.e2y, tr.e2z), tr.eps, t, u, v)) continue;
+				if(!(tr.flags & vis_bit)) continue;
+				if(!y4_accept_t<KIND>(t, t_lo, t_hi, tr.prim, hit.prim)) continue;
+				hit.t = t; hit.bu = u; hit.bv = v; hit.prim = (int32_t) tr.prim;
+				if(KIND == Y4_TRACE_CLOSEST) t_hi = t;
+				else { done = true; break; }
+			}
+			if(!done && (ngroup.y & 0xff000000u) == 0u)
+			{
+				if(sp == 0) done = true;
+				else ngroup = stack[--sp];
+			}
+			if(done)
+			{
+				float4 o; o.x = hit.t; o.y = hit.bu; o.z = hit.bv; o.w = __int_as_float(hit.prim);
+				*reinterpret_cast<float4 *>(out + ray_i) = o;
+				have = false;
+				break;
+			}
+			if(__popc(__activemask()) < leave_below) break;
+		}
+		__syncwarp();
 	}
 	if(COUNT)
 	{
@@ -91,17 +178,24 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, con
 	}
 }
 
+template<int KIND, bool COUNT, int MINB>
+int launch_k(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out)
+{
+	int per_sm = 0;
+	Y4_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<KIND, COUNT, MINB>, kTraceThreads, 0));
+	if(per_sm < 1) per_sm = 1;
+	const uint64_t want = (n + kTraceThreads - 1) / kTraceThreads;
+	const uint64_t full = (uint64_t) ctx->sm_count * per_sm;     // persistent: one wave of resident CTAs
+	const int grid = (int) (want < full ? want : full);
+	k_trace<KIND, COUNT, MINB><<<grid, kTraceThreads, 0, ctx->stream>>>(ctx->view(), d_rays, n, d_out, reinterpret_cast<unsigned long long *>(ctx->d_work_counter),
+	                                                                   ctx->d_visit_counters, ctx->fetch_threshold, ctx->postpone_div);
+	return Y4GPU_OK;
+}
 template<int KIND, bool COUNT>
 int launch(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out)
 {
-	int per_sm = 0;
-	Y4_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<KIND, COUNT>, kTraceThreads, 0));
-	if(per_sm < 1) per_sm = 1;
-	const uint64_t want = (n + kTraceThreads - 1) / kTraceThreads;
-	const uint64_t full = (uint64_t) ctx->sm_count * per_sm;
-	const int grid = (int) (want < full ? want : full);
-	k_trace<KIND, COUNT><<<grid, kTraceThreads, 0, ctx->stream>>>(ctx->view(), d_rays, n, d_out, ctx->d_work_counter, ctx->d_visit_counters);
-	return Y4GPU_OK;
+	if(COUNT) return launch_k<KIND, true, 3>(ctx, d_rays, n, d_out);
+	return ctx->min_blocks >= 4 ? launch_k<KIND, false, 4>(ctx, d_rays, n, d_out) : launch_k<KIND, false, 3>(ctx, d_rays, n, d_out);
 }
 
 } // namespace
@@ -110,7 +204,7 @@ int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays,
 {
 	if(n == 0) return Y4GPU_OK;
 	cudaStream_t st = ctx->stream;
-	Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_work_counter, 0, sizeof(uint32_t), st));
+	Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_work_counter, 0, sizeof(unsigned long long), st));
 	if(counted) Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_visit_counters, 0, 2 * sizeof(unsigned long long), st));
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
 	int rc;

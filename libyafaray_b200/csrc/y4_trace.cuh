@@ -17,6 +17,7 @@ struct Y4Bvh8
 	const Y4U4 *nodes;     // 5 words per node, root = node 0
 	const Y4Tri *tris;     // leaf-ordered triangle records
 	uint32_t n_tris;       // 0 => empty scene
+	const uint32_t *consts; // device: [0] = 0x4B000000 (see y4_byte_m); unused on the host
 };
 
 struct Y4TraceStats { uint32_t nodes, tris; };
@@ -96,16 +97,72 @@ Y4_HD Y4Tri y4_ld_tri(const Y4Tri *p)
 #endif
 }
 Y4_HD uint32_t y4_byte(uint32_t w, int i) { return (w >> (8 * i)) & 0xffu; }
+// v << (s mod 32): SHF.L.W wraps the shift amount in hardware
+Y4_HD uint32_t y4_shl_wrap(uint32_t v, uint32_t s)
+{
+#if defined(__CUDA_ARCH__)
+	return __funnelshift_l(0u, v, s);
+#else
+	return v << (s & 31u);
+#endif
+}
+
+// Quantised byte i of w -> float WITHOUT an int->float conversion (I2F is quarter-rate): one
+// PRMT drops the byte into mantissa bits 8..15 of 2^23, giving f = 2^23 + 256*q exactly.  The
+// slab plane then is t = q*a + b = f*(a/256) + (b - 2^15*a): one FFMA with pre-folded per-axis
+// coefficients (y4_node_hits).  The folded offset is rounded once (error <= |a|/512, i.e. 1/512
+// of a quantisation step), which the coefficients absorb conservatively.
+// `magic` must hold 0x4B000000 in a REGISTER so that the PRMT selector can be the immediate: ptxas
+// folds any compile-time constant into the instruction's only immediate slot and then spends an
+// extra IMAD per PRMT materialising selectors.  The kernels therefore load it from memory once
+// (Y4Bvh8::consts[0]); it is a scheduling aid, not data.
+Y4_HD float y4_byte_m(uint32_t w, int i, uint32_t magic)
+{
+#if defined(__CUDA_ARCH__)
+	return __uint_as_float(__byte_perm(w, magic, 0x7604u + ((uint32_t) i << 4)));
+#else
+	return y4_u2f(magic | (((w >> (8 * i)) & 0xffu) << 8));
+#endif
+}
+// Per-ray constants of the node test.
+struct Y4RayCtx
+{
+	V3 o, d, idir;
+	uint32_t oct_inv;    // bit2/1/0 set where d.x/y/z >= 0
+};
+Y4_HD Y4RayCtx y4_ray_ctx(const V3 o, const V3 d)
+{
+	Y4RayCtx c; c.o = o; c.d = d;
+	c.idir = v3(y4_safe_rcp(d.x), y4_safe_rcp(d.y), y4_safe_rcp(d.z));
+	c.oct_inv = (d.x >= 0.f ? 4u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 1u : 0u);
+	return c;
+}
+
+// Folded slab coefficients of one axis: t_near = f*an + bn (biased early by 1/256 step),
+// t_far = f*af + bf (scaled by 1 + 2^-21 and biased late), f = y4_byte_m(...).
+struct Y4Axis { float an, bn, af, bf; };
+Y4_HD Y4Axis y4_axis(float scale, float origin, float o, float idir)
+{
+	const float a = scale * idir;                 // t per quantisation step
+	const float b = (origin - o) * idir;          // t of the node frame origin
+	const float a8 = a * (1.f / 256.f);
+	const float slack = fabsf(a8);                // 1/256 step, covers the folding error (<= |a|/512)
+	const float k_far = 1.0000005f;
+	Y4Axis r;
+	r.an = a8; r.bn = (b - 32768.f * a) - slack;
+	r.af = a8 * k_far; r.bf = (b - 32768.f * a) * k_far + slack * 1.5f;
+	return r;
+}
 
 // Intersect one node's 8 quantised child boxes; returns the hit mask in "priority" bit
 // positions: internal children at bits 24 + (slot ^ oct_inv), leaf triangles at their
 // tri_base-relative offsets.
 Y4_HD uint32_t y4_node_hits(const Y4U4 w0, const Y4U4 w1, const Y4U4 w2, const Y4U4 w3, const Y4U4 w4,
-                            const V3 o, const V3 idir, const uint32_t oct_inv, const float t_lo, const float t_hi)
+                            const V3 o, const V3 idir, const uint32_t oct_inv, const float t_lo, const float t_hi, const uint32_t magic)
 {
-	const float sx = y4_u2f((w0.w & 0xffu) << 23), sy = y4_u2f(((w0.w >> 8) & 0xffu) << 23), sz = y4_u2f(((w0.w >> 16) & 0xffu) << 23);
-	const float ax = sx * idir.x, ay = sy * idir.y, az = sz * idir.z;
-	const float bx = (y4_u2f(w0.x) - o.x) * idir.x, by = (y4_u2f(w0.y) - o.y) * idir.y, bz = (y4_u2f(w0.z) - o.z) * idir.z;
+	const Y4Axis X = y4_axis(y4_u2f((w0.w & 0xffu) << 23), y4_u2f(w0.x), o.x, idir.x);
+	const Y4Axis Y = y4_axis(y4_u2f(((w0.w >> 8) & 0xffu) << 23), y4_u2f(w0.y), o.y, idir.y);
+	const Y4Axis Z = y4_axis(y4_u2f(((w0.w >> 16) & 0xffu) << 23), y4_u2f(w0.z), o.z, idir.z);
 	const bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
 	uint32_t hits = 0;
 #if defined(__CUDA_ARCH__)
@@ -113,7 +170,9 @@ Y4_HD uint32_t y4_node_hits(const Y4U4 w0, const Y4U4 w1, const Y4U4 w2, const Y
 #endif
 	for(int h = 0; h < 2; ++h)
 	{
-		const uint32_t meta4 = h ? w1.w : w1.z;
+		uint32_t meta4 = h ? w1.w : w1.z;
+		// internal children carry 0b001_11sss: XOR their slot with the ray octant, 4 bytes at a time
+		meta4 ^= (((meta4 & (meta4 >> 1)) >> 3) & 0x01010101u) * oct_inv;
 		const uint32_t qlx = h ? w2.y : w2.x, qly = h ? w2.w : w2.z, qlz = h ? w3.y : w3.x;
 		const uint32_t qhx = h ? w3.w : w3.z, qhy = h ? w4.y : w4.x, qhz = h ? w4.w : w4.z;
 		const uint32_t nearx = nx ? qhx : qlx, farx = nx ? qlx : qhx;
@@ -124,21 +183,31 @@ Y4_HD uint32_t y4_node_hits(const Y4U4 w0, const Y4U4 w1, const Y4U4 w2, const Y
 #endif
 		for(int i = 0; i < 4; ++i)
 		{
-			const uint32_t m = y4_byte(meta4, i);
-			const float t0x = (float) y4_byte(nearx, i) * ax + bx, t1x = (float) y4_byte(farx, i) * ax + bx;
-			const float t0y = (float) y4_byte(neary, i) * ay + by, t1y = (float) y4_byte(fary, i) * ay + by;
-			const float t0z = (float) y4_byte(nearz, i) * az + bz, t1z = (float) y4_byte(farz, i) * az + bz;
+			const float t0x = fmaf(y4_byte_m(nearx, i, magic), X.an, X.bn), t1x = fmaf(y4_byte_m(farx, i, magic), X.af, X.bf);
+			const float t0y = fmaf(y4_byte_m(neary, i, magic), Y.an, Y.bn), t1y = fmaf(y4_byte_m(fary, i, magic), Y.af, Y.bf);
+			const float t0z = fmaf(y4_byte_m(nearz, i, magic), Z.an, Z.bn), t1z = fmaf(y4_byte_m(farz, i, magic), Z.af, Z.bf);
 			const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, t_lo));
 			const float tf = fminf(fminf(t1x, t1y), fminf(t1z, t_hi));
-			if(tn <= tf * 1.0000005f && m != 0u)
+			if(tn <= tf)
 			{
-				const uint32_t is_inner = ((m & 0x18u) == 0x18u) ? 1u : 0u;   // low5 in 24..31
-				const uint32_t bit = (m ^ (is_inner ? oct_inv : 0u)) & 31u;
-				hits |= (m >> 5) << bit;
+				const uint32_t m = y4_byte(meta4, i);     // empty slot: m == 0 contributes nothing
+				hits |= y4_shl_wrap(m >> 5, m);
 			}
 		}
 	}
 	return hits;
+}
+
+// Interval rule.  Closest: tmin <= t < best (accelerator_kdtree.cc:731); among *exactly* equal t the
+// lower primitive index wins, which makes the result independent of traversal order (the
+// reference keeps whichever its kd-leaf order tests first: the documented near-tie class).
+// Shadow / transparent shadow: t_lo <= t < t_max (:867, :1019).
+template<int KIND>
+Y4_HD bool y4_accept_t(float t, float t_lo, float t_hi, uint32_t prim, int32_t best_prim)
+{
+	if(!(t >= t_lo)) return false;
+	if(t < t_hi) return true;
+	return KIND == Y4_TRACE_CLOSEST && t == t_hi && best_prim >= 0 && (int32_t) prim < best_prim;
 }
 
 // Full traversal of one ray.  KIND is a compile-time constant in the kernels.
@@ -157,6 +226,11 @@ Y4_HD void y4_trace_ray(const Y4Bvh8 &bvh, const Y4PreparedRay &ray, Y4Hit &hit,
 	const uint32_t oct_inv = (ray.d.x >= 0.f ? 4u : 0u) | (ray.d.y >= 0.f ? 2u : 0u) | (ray.d.z >= 0.f ? 1u : 0u);
 	float t_hi = ray.t_hi;
 	int sp = 0;
+#if defined(__CUDA_ARCH__)
+	const uint32_t magic = __ldg(bvh.consts);
+#else
+	const uint32_t magic = 0x4B000000u;
+#endif
 	// virtual parent of the root: child_base 0, imask = slot 0, hit bit at slot 0's priority
 	uint2 ngroup; ngroup.x = 0u; ngroup.y = (1u << (24u + oct_inv)) | 1u;
 	while(true)
@@ -173,7 +247,7 @@ Y4_HD void y4_trace_ray(const Y4Bvh8 &bvh, const Y4PreparedRay &ray, Y4Hit &hit,
 			const Y4U4 *n = bvh.nodes + (size_t) child * Y4_NODE_WORDS;
 			const Y4U4 w0 = y4_ld_u4(n), w1 = y4_ld_u4(n + 1), w2 = y4_ld_u4(n + 2), w3 = y4_ld_u4(n + 3), w4 = y4_ld_u4(n + 4);
 			if(stats) stats->nodes++;
-			const uint32_t hits = y4_node_hits(w0, w1, w2, w3, w4, ray.o, idir, oct_inv, ray.t_lo, t_hi);
+			const uint32_t hits = y4_node_hits(w0, w1, w2, w3, w4, ray.o, idir, oct_inv, ray.t_lo, t_hi, magic);
 			ngroup.x = w1.x; ngroup.y = (hits & 0xff000000u) | (w0.w >> 24);
 			tgroup.x = w1.y; tgroup.y = hits & 0x00ffffffu;
 		}
@@ -190,8 +264,8 @@ Y4_HD void y4_trace_ray(const Y4Bvh8 &bvh, const Y4PreparedRay &ray, Y4Hit &hit,
 			if(stats) stats->tris++;
 			float t, u, v;
 			if(!y4_tri_intersect(ray.o, ray.d, v3(tr.v0x, tr.v0y, tr.v0z), v3(tr.e1x, tr.e1y, tr.e1z), v3(tr.e2x, tr.e2y, tr.e2z), tr.eps, t, u, v)) continue;
-			if(!(t < t_hi && t >= ray.t_lo)) continue;
 			if(!(tr.flags & vis_bit)) continue;
+			if(!y4_accept_t<KIND>(t, ray.t_lo, t_hi, tr.prim, hit.prim)) continue;
 			if(KIND == Y4_TRACE_CLOSEST)
 			{
 				t_hi = t; hit.t = t; hit.bu = u; hit.bv = v; hit.prim = (int32_t) tr.prim;
