@@ -27,15 +27,17 @@ def main():
     ref_hits = {}
     first = True
     for cfg in grid.split(";"):
-        f, p, m = (int(x) for x in cfg.split(","))
+        vals = [int(x) for x in cfg.split(",")]
+        f, p, m = vals[:3]
+        leaf = vals[3] if len(vals) > 3 else 0
         os.environ["Y4GPU_FETCH_THRESHOLD"], os.environ["Y4GPU_POSTPONE_DIV"], os.environ["Y4GPU_MIN_BLOCKS"] = str(f), str(p), str(m)
-        acc = AcceleratorB200(tris)
+        acc = AcceleratorB200(tris, leaf_max=leaf)
         if first:
             acc.intersect(rays["primary"], hits)
             acc.synchronize()
             rays["shadow"], rays["diffuse"] = bench.gen_secondary(torch, tris_d, rays["primary"], hits, seed=0xD1F)
             first = False
-        row = {"fetch": f, "postpone": p, "minb": m}
+        row = {"fetch": f, "postpone": p, "minb": m, "leaf": leaf, "n_nodes": acc.stats()["n_nodes"]}
         for b in bench.BATCHES:
             fn = acc.isShadowed if b == "shadow" else acc.intersect
             ms = []
