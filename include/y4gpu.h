@@ -115,6 +115,110 @@ int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int m
 int y4gpu_get_stats(const y4gpu_ctx *ctx, y4gpu_stats *out);
 int y4gpu_synchronize(y4gpu_ctx *ctx);
 
+
+/* ===================================================================================== */
+/* Wavefront path tracer: PathIntegrator::integrate + TiledIntegrator::renderPass/renderTile
+ * + ImageFilm::addSample on the device.
+ *
+ * Reference interfaces replaced (libYafaRay tree):
+ *   y4gpu_pt_set_scene   <- what PathIntegrator::preprocess caches (camera_, lights_, background_,
+ *                           aa params; src/integrator/integrator.cc:62-90,
+ *                           integrator_path_tracer.cc:52-118,292-366) in PARAMETER form: the library
+ *                           derives camera axes, light frames, material component weights and the film
+ *                           filter table itself with the reference's fp32 operation order
+ *                           (camera.cc:51-71, camera_perspective.cc:28-69, light_area.cc:33-52,
+ *                           material_shiny_diffuse.cc:39-82, imagefilm.cc:129-173)
+ *   y4gpu_pt_render_pass <- TiledIntegrator::renderPass(samples, offset, adaptive, aa_pass)
+ *                           (integrator_tiled.cc:236-408) incl. ImageFilm::addSample (imagefilm.cc:680-733)
+ *   y4gpu_pt_read_film   <- the weights_ / Combined-layer buffers ImageFilm::flush normalises
+ *                           (imagefilm.cc:590-617)
+ * Scene features outside the supported set are rejected with Y4GPU_ERR_UNSUPPORTED.            */
+
+enum { Y4GPU_MAT_SHINYDIFFUSE = 0, Y4GPU_MAT_LIGHT = 1 };
+typedef struct y4gpu_pt_material
+{
+	int32_t type;                 /* Y4GPU_MAT_* */
+	float color[3];               /* shinydiffusemat `color` / light_mat `color` */
+	float diffuse_reflect;        /* shinydiffusemat: `diffuse_reflect` (default 1) */
+	float emit;                   /* shinydiffusemat: `emit`; light_mat: `power` */
+	int32_t oren_nayar;           /* diffuse_brdf == "oren_nayar" */
+	float sigma;                  /* oren-nayar sigma */
+	int32_t double_sided;         /* light_mat */
+	int32_t receive_shadows;      /* default 1 */
+	int32_t flat_material;        /* default 0 */
+	int32_t reserved[5];
+} y4gpu_pt_material;
+
+enum { Y4GPU_LIGHT_POINT = 0, Y4GPU_LIGHT_AREA = 1 };
+typedef struct y4gpu_pt_light
+{
+	int32_t type;                 /* Y4GPU_LIGHT_* ; lights in the reference's (name-sorted) order */
+	float from[3];                /* pointlight `from` / arealight `corner` */
+	float point1[3], point2[3];   /* arealight */
+	float color[3];
+	float power;
+	int32_t samples;              /* arealight `samples` */
+	int32_t cast_shadows;         /* default 1 */
+	int32_t reserved[4];
+} y4gpu_pt_light;
+
+typedef struct y4gpu_pt_camera    /* `perspective` camera parameters (camera_perspective.cc:182-220) */
+{
+	float from[3], to[3], up[3];
+	int32_t resx, resy;
+	float aspect_ratio, focal, aperture, dof_distance, near_clip, far_clip;
+	int32_t reserved[4];
+} y4gpu_pt_camera;
+
+enum { Y4GPU_FILTER_BOX = 0, Y4GPU_FILTER_GAUSS = 1, Y4GPU_FILTER_MITCHELL = 2, Y4GPU_FILTER_LANCZOS = 3 };
+typedef struct y4gpu_pt_params
+{
+	/* integrator (integrator_path_tracer.cc:292-366) */
+	int32_t bounces, path_samples, russian_roulette_min_bounces, no_recursive;
+	int32_t transp_background;
+	float background[3];          /* constant background colour * power */
+	/* render parameters (scene.cc:528-644, imagefilm.cc:45-127) */
+	int32_t width, height, xstart, ystart;
+	int32_t aa_passes, aa_samples, aa_inc_samples;
+	float aa_sample_multiplier_factor, aa_light_sample_multiplier_factor;
+	float aa_pixelwidth, aa_clamp_samples;
+	int32_t filter_type;          /* Y4GPU_FILTER_* */
+	int32_t shadow_bias_auto; float shadow_bias;        /* adv_auto_shadow_bias_enabled / adv_shadow_bias_value */
+	int32_t min_raydist_auto; float min_raydist;        /* adv_auto_min_raydist_enabled / adv_min_raydist_value */
+	uint32_t base_sampling_offset;                      /* adv_base_sampling_offset + 100000 * adv_computer_node */
+	uint32_t rr_seed;             /* seed of the per-path Russian-roulette hash (the reference uses rand()) */
+	uint32_t wave_size;           /* pixel-samples processed per wavefront (0 = default 2^21) */
+	int32_t reserved[7];
+} y4gpu_pt_params;
+
+typedef struct y4gpu_pt_stats
+{
+	uint64_t samples;             /* pixel-samples rendered by the last pass */
+	uint64_t rays_closest, rays_shadow;
+	uint64_t kernel_launches;     /* kernels launched by the last pass */
+	double pass_ms;               /* device time of the last pass (CUDA events) */
+	uint64_t reserved[4];
+} y4gpu_pt_stats;
+
+/* Per-triangle material index travels in the flag word of y4gpu_upload_triangles (bits 8..31).
+ * vertex_normals: n_tri*9 floats (exported normals: shading normal interpolated like
+ * primitive_triangle.cc:104-114) or NULL for flat shading. */
+int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_pt_material *mats, uint32_t n_mat,
+                       const y4gpu_pt_light *lights, uint32_t n_light, const y4gpu_pt_params *params,
+                       const float *vertex_normals);
+/* Optional: accumulate into caller-owned device buffers (weights: h*w floats, rgba: h*w*4 floats), e.g.
+ * a tensor that is then summed across GPUs with one NCCL all-reduce per pass.  NULL = internal film. */
+int y4gpu_pt_set_film_buffers(y4gpu_ctx *ctx, float *d_weights, float *d_rgba);
+int y4gpu_pt_clear_film(y4gpu_ctx *ctx);
+/* Renders samples [offset, offset + n_samples) of every pixel (or of the listed pixels: pixel_list
+ * holds y*width+x entries of the pixels ImageFilm::doMoreSamples flags, host or device memory).
+ * This GPU renders the sample indices s with (s - offset) % shard_count == shard_index. */
+int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, int aa_pass_number,
+                         const uint32_t *pixel_list, uint64_t n_pixels, int shard_index, int shard_count);
+/* Film as accumulated (NOT normalised): weights h*w, rgba h*w*4; host or device destinations. */
+int y4gpu_pt_read_film(y4gpu_ctx *ctx, float *weights, float *rgba);
+int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out);
+
 #ifdef __cplusplus
 }
 #endif

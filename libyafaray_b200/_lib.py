@@ -37,6 +37,45 @@ class Stats(C.Structure):
     ]  # fmt: skip
 
 
+class PtMaterial(C.Structure):
+    _fields_ = [("type", C.c_int32), ("color", C.c_float * 3), ("diffuse_reflect", C.c_float), ("emit", C.c_float),
+                ("oren_nayar", C.c_int32), ("sigma", C.c_float), ("double_sided", C.c_int32), ("receive_shadows", C.c_int32),
+                ("flat_material", C.c_int32), ("reserved", C.c_int32 * 5)]  # fmt: skip
+
+
+class PtLight(C.Structure):
+    _fields_ = [("type", C.c_int32), ("from_", C.c_float * 3), ("point1", C.c_float * 3), ("point2", C.c_float * 3),
+                ("color", C.c_float * 3), ("power", C.c_float), ("samples", C.c_int32), ("cast_shadows", C.c_int32),
+                ("reserved", C.c_int32 * 4)]  # fmt: skip
+
+
+class PtCamera(C.Structure):
+    _fields_ = [("from_", C.c_float * 3), ("to", C.c_float * 3), ("up", C.c_float * 3), ("resx", C.c_int32), ("resy", C.c_int32),
+                ("aspect_ratio", C.c_float), ("focal", C.c_float), ("aperture", C.c_float), ("dof_distance", C.c_float),
+                ("near_clip", C.c_float), ("far_clip", C.c_float), ("reserved", C.c_int32 * 4)]  # fmt: skip
+
+
+class PtParams(C.Structure):
+    _fields_ = [("bounces", C.c_int32), ("path_samples", C.c_int32), ("russian_roulette_min_bounces", C.c_int32), ("no_recursive", C.c_int32),
+                ("transp_background", C.c_int32), ("background", C.c_float * 3),
+                ("width", C.c_int32), ("height", C.c_int32), ("xstart", C.c_int32), ("ystart", C.c_int32),
+                ("aa_passes", C.c_int32), ("aa_samples", C.c_int32), ("aa_inc_samples", C.c_int32),
+                ("aa_sample_multiplier_factor", C.c_float), ("aa_light_sample_multiplier_factor", C.c_float),
+                ("aa_pixelwidth", C.c_float), ("aa_clamp_samples", C.c_float), ("filter_type", C.c_int32),
+                ("shadow_bias_auto", C.c_int32), ("shadow_bias", C.c_float), ("min_raydist_auto", C.c_int32), ("min_raydist", C.c_float),
+                ("base_sampling_offset", C.c_uint32), ("rr_seed", C.c_uint32), ("wave_size", C.c_uint32), ("reserved", C.c_int32 * 7)]  # fmt: skip
+
+
+class PtStats(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("pass_ms", C.c_double), ("reserved", C.c_uint64 * 4)]  # fmt: skip
+
+
+MAT_SHINYDIFFUSE, MAT_LIGHT = 0, 1
+LIGHT_POINT, LIGHT_AREA = 0, 1
+FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
+
+
 class Y4Error(RuntimeError):
     pass
 
@@ -50,6 +89,8 @@ EXPORTED = [
     "y4gpu_upload_triangles", "y4gpu_build", "y4gpu_get_bound",
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow",
     "y4gpu_get_stats", "y4gpu_synchronize",
+    "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
+    "y4gpu_pt_read_film", "y4gpu_pt_get_stats",
 ]  # fmt: skip
 
 
@@ -92,6 +133,18 @@ def lib() -> C.CDLL:
     L.y4gpu_get_stats.restype = i32
     L.y4gpu_synchronize.argtypes = [vp]
     L.y4gpu_synchronize.restype = i32
+    L.y4gpu_pt_set_scene.argtypes = [vp, C.POINTER(PtCamera), C.POINTER(PtMaterial), u32, C.POINTER(PtLight), u32, C.POINTER(PtParams), vp]
+    L.y4gpu_pt_set_scene.restype = i32
+    L.y4gpu_pt_set_film_buffers.argtypes = [vp, vp, vp]
+    L.y4gpu_pt_set_film_buffers.restype = i32
+    L.y4gpu_pt_clear_film.argtypes = [vp]
+    L.y4gpu_pt_clear_film.restype = i32
+    L.y4gpu_pt_render_pass.argtypes = [vp, i32, i32, i32, vp, u64, i32, i32]
+    L.y4gpu_pt_render_pass.restype = i32
+    L.y4gpu_pt_read_film.argtypes = [vp, vp, vp]
+    L.y4gpu_pt_read_film.restype = i32
+    L.y4gpu_pt_get_stats.argtypes = [vp, C.POINTER(PtStats)]
+    L.y4gpu_pt_get_stats.restype = i32
     _lib = L
     return L
 

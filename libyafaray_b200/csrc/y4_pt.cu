@@ -1,7 +1,361 @@
-// Wavefront path tracer back end (PathIntegrator on the GPU).  See y4_pt_*.cuh.
+// Wavefront path tracer back end (PathIntegrator on the GPU): scene derivation on the host,
+// stage kernels, the per-pass launch sequence and the film.  Per-path logic: y4_pt_stages.cuh.
 #include "y4_ctx.h"
+#include "y4_pt_stages.cuh"
+#include "y4_faure.h"
+#include <cstring>
+#include <vector>
 
-extern "C" void y4gpu_pt_release(y4gpu_ctx *ctx)
+struct Y4Pt
 {
-	(void) ctx;
+	Y4PtScene h_scene;                 // host copy (device pointers inside)
+	Y4PtScene *d_scene = nullptr;
+	Y4PtMaterial *d_mats = nullptr;
+	float *d_normals = nullptr;
+	uint8_t *d_sigma = nullptr; uint16_t *d_offset = nullptr, *d_prime = nullptr; double *d_inv_prime = nullptr;
+	bool scene_set = false;
+	y4gpu_pt_params params = {};
+	int max_light_samples = 1;
+	// film
+	float *d_film_w = nullptr, *d_film_rgba = nullptr;      // in use
+	float *own_film_w = nullptr, *own_film_rgba = nullptr;  // owned (when the caller gave none)
+	// wave state
+	uint32_t cap = 0;
+	Y4PtWave wave = {};
+	void *wave_mem = nullptr;
+	uint32_t *d_pixel_list = nullptr; uint64_t pixel_list_cap = 0;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	y4gpu_pt_stats stats = {};
+};
+
+#include "y4_pt_host.h"
+
+// ---- kernels: one thread per pixel-sample of the wave, grid-stride ----------------------------------
+namespace {
+
+constexpr int kPtThreads = 256;
+
+__global__ void __launch_bounds__(kPtThreads) k_pt_fill(Y4PtWave W, const uint32_t *__restrict__ pixel_list, uint64_t first, uint32_t ns_local, int shard_index, int shard_count)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x)
+	{
+		const uint64_t g = first + i;
+		const uint64_t slot = g / ns_local;
+		W.pix[i] = pixel_list ? pixel_list[slot] : (uint32_t) slot;
+		W.samp[i] = (uint32_t) shard_index + (uint32_t) (g % ns_local) * (uint32_t) shard_count;
+	}
+}
+__global__ void __launch_bounds__(kPtThreads) k_pt_gen(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_gen(*sc, W, ps, i);
+}
+__global__ void __launch_bounds__(kPtThreads) k_pt_primary(const Y4PtScene *__restrict__ sc, Y4PtWave W)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_primary(*sc, W, i);
+}
+__global__ void __launch_bounds__(kPtThreads) k_pt_direct(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, int all_lights, int light, int k)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_direct(*sc, W, ps, i, all_lights != 0, light, k);
+}
+__global__ void __launch_bounds__(kPtThreads) k_pt_direct_resolve(const Y4PtScene *__restrict__ sc, Y4PtWave W, int all_lights, int light, int k)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_direct_resolve(*sc, W, i, all_lights != 0, light, k);
+}
+__global__ void __launch_bounds__(kPtThreads) k_pt_bounce_sample(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, int depth, int sub)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_bounce_sample(*sc, W, ps, i, depth, sub);
+}
+__global__ void __launch_bounds__(kPtThreads) k_pt_bounce_hit(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, int depth, int sub)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_bounce_hit(*sc, W, ps, i, depth, sub);
+}
+__global__ void __launch_bounds__(kPtThreads) k_pt_splat(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, float *film_w, float *film_rgba)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_finish_splat(*sc, W, ps, i, film_w, film_rgba);
+}
+
+inline int pt_grid(const y4gpu_ctx *ctx, uint32_t n)
+{
+	const uint32_t want = (n + kPtThreads - 1) / kPtThreads, full = (uint32_t) ctx->sm_count * 8u;
+	return (int) (want < full ? (want ? want : 1u) : full);
+}
+
+void pt_free_wave(Y4Pt *pt)
+{
+	cudaFree(pt->wave_mem); pt->wave_mem = nullptr; pt->cap = 0;
+}
+
+// One allocation carved into the SoA arrays of the wave (all 16-byte aligned).
+int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt *pt, uint32_t cap)
+{
+	if(cap <= pt->cap) return Y4GPU_OK;
+	pt_free_wave(pt);
+	const size_t n = cap;
+	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 32 + 16 + 16 /*ray hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/) + 256;
+	Y4_CUDA(ctx, cudaMalloc(&pt->wave_mem, bytes));
+	char *p = (char *) pt->wave_mem;
+	auto take = [&](size_t b) { char *r = p; p += (b + 15) & ~(size_t) 15; return (void *) r; };
+	Y4PtWave &W = pt->wave;
+	W.col = (float *) take(n * 16); W.pcol = (float *) take(n * 16); W.thr = (float *) take(n * 16); W.lcol = (float *) take(n * 16);
+	W.acc_a = (float *) take(n * 16); W.acc_b = (float *) take(n * 16);
+	W.ray = (Y4Ray *) take(n * 32); W.hit = (Y4Hit *) take(n * 16); W.hit0 = (Y4Hit *) take(n * 16);
+	W.sray = (Y4Ray *) take(2 * n * 32); W.shit = (Y4Hit *) take(2 * n * 16); W.scontrib = (float *) take(2 * n * 16);
+	W.pix = (uint32_t *) take(n * 4); W.samp = (uint32_t *) take(n * 4); W.flags = (uint32_t *) take(n * 4); W.lnum = (uint32_t *) take(n * 4);
+	pt->cap = cap;
+	return Y4GPU_OK;
+}
+
+} // namespace
+
+static bool pt_is_device_ptr(const void *p)
+{
+	cudaPointerAttributes a;
+	if(cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+	return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+extern "C" {
+
+void y4gpu_pt_release(y4gpu_ctx *ctx)
+{
+	Y4Pt *pt = ctx->pt;
+	if(!pt) return;
+	pt_free_wave(pt);
+	cudaFree(pt->d_scene); cudaFree(pt->d_mats); cudaFree(pt->d_normals);
+	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime);
+	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); cudaFree(pt->d_pixel_list);
+	if(pt->ev0) cudaEventDestroy(pt->ev0);
+	if(pt->ev1) cudaEventDestroy(pt->ev1);
+	delete pt;
+	ctx->pt = nullptr;
+}
+
+int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_pt_material *mats, uint32_t n_mat,
+                       const y4gpu_pt_light *lights, uint32_t n_light, const y4gpu_pt_params *params, const float *vertex_normals)
+{
+	if(!ctx || !cam || !params || (n_mat && !mats) || (n_light && !lights)) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	if(!ctx->built) { ctx->err = "y4gpu_pt_set_scene before y4gpu_build"; return Y4GPU_ERR_ARG; }
+	// ---- the supported set; everything else is rejected, never approximated ----
+	if(n_mat == 0) { ctx->err = "no materials"; return Y4GPU_ERR_ARG; }
+	if(n_light > Y4_PT_MAX_LIGHTS) { ctx->err = "more than 64 lights"; return Y4GPU_ERR_UNSUPPORTED; }
+	if(cam->aperture != 0.f) { ctx->err = "depth of field (aperture != 0) is not supported by the GPU back end"; return Y4GPU_ERR_UNSUPPORTED; }
+	if(params->bounces < 1 || params->bounces > 11) { ctx->err = "bounces must be 1..11 (sample dimensions 4*depth+4 < 50)"; return Y4GPU_ERR_UNSUPPORTED; }
+	if(params->path_samples < 1 || params->width < 1 || params->height < 1) { ctx->err = "bad path_samples / film size"; return Y4GPU_ERR_ARG; }
+	for(uint32_t i = 0; i < n_mat; ++i)
+		if(mats[i].type != Y4GPU_MAT_SHINYDIFFUSE && mats[i].type != Y4GPU_MAT_LIGHT) { ctx->err = "unsupported material type"; return Y4GPU_ERR_UNSUPPORTED; }
+	for(uint32_t i = 0; i < n_light; ++i)
+		if(lights[i].type != Y4GPU_LIGHT_POINT && lights[i].type != Y4GPU_LIGHT_AREA) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	if(!ctx->pt) ctx->pt = new Y4Pt;
+	Y4Pt *pt = ctx->pt;
+	if(!pt->ev0) { Y4_CUDA(ctx, cudaEventCreate(&pt->ev0)); Y4_CUDA(ctx, cudaEventCreate(&pt->ev1)); }
+	cudaStream_t st = ctx->stream;
+	Y4PtScene &sc = pt->h_scene;
+	memset(&sc, 0, sizeof(sc));
+	sc.cam = derive_camera(*cam);
+	sc.bounces = params->bounces; sc.n_paths = params->path_samples; sc.rr_min_bounces = params->russian_roulette_min_bounces;
+	sc.no_recursive = params->no_recursive; sc.transp_background = params->transp_background;
+	sc.background = c3(params->background[0], params->background[1], params->background[2]);
+	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
+	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
+	sc.base_sampling_offset = params->base_sampling_offset; sc.rr_seed = params->rr_seed;
+	sc.aa_light_sample_multiplier = 1.f;
+	sc.aa_passes = params->aa_passes;
+	sc.width = params->width; sc.height = params->height; sc.cx0 = params->xstart; sc.cy0 = params->ystart;
+	sc.clamp_samples = params->aa_clamp_samples;
+	derive_film(*params, sc);
+	sc.n_lights = (int) n_light; sc.n_mats = (int) n_mat;
+	pt->max_light_samples = 1;
+	for(uint32_t i = 0; i < n_light; ++i)
+	{
+		sc.lights[i] = derive_light(lights[i]);
+		const int ns = y4_light_num_samples(sc, sc.lights[i]);
+		if(ns > pt->max_light_samples) pt->max_light_samples = ns;
+	}
+	std::vector<Y4PtMaterial> hm(n_mat);
+	for(uint32_t i = 0; i < n_mat; ++i) hm[i] = derive_material(mats[i]);
+	cudaFree(pt->d_mats); pt->d_mats = nullptr;
+	Y4_CUDA(ctx, cudaMalloc(&pt->d_mats, n_mat * sizeof(Y4PtMaterial)));
+	Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_mats, hm.data(), n_mat * sizeof(Y4PtMaterial), cudaMemcpyHostToDevice, st));
+	cudaFree(pt->d_normals); pt->d_normals = nullptr;
+	if(vertex_normals && ctx->n_tri)
+	{
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_normals, ctx->n_tri * 9 * sizeof(float)));
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_normals, vertex_normals, ctx->n_tri * 9 * sizeof(float), cudaMemcpyDefault, st));
+	}
+	if(!pt->d_sigma)
+	{
+		const Y4FaureHost fh = y4_faure_build();
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_sigma, fh.sigma.size())); Y4_CUDA(ctx, cudaMalloc(&pt->d_offset, sizeof(fh.offset)));
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_prime, sizeof(fh.prime))); Y4_CUDA(ctx, cudaMalloc(&pt->d_inv_prime, sizeof(fh.inv_prime)));
+		Y4_CUDA(ctx, cudaMemcpy(pt->d_sigma, fh.sigma.data(), fh.sigma.size(), cudaMemcpyHostToDevice));
+		Y4_CUDA(ctx, cudaMemcpy(pt->d_offset, fh.offset, sizeof(fh.offset), cudaMemcpyHostToDevice));
+		Y4_CUDA(ctx, cudaMemcpy(pt->d_prime, fh.prime, sizeof(fh.prime), cudaMemcpyHostToDevice));
+		Y4_CUDA(ctx, cudaMemcpy(pt->d_inv_prime, fh.inv_prime, sizeof(fh.inv_prime), cudaMemcpyHostToDevice));
+	}
+	sc.mats = pt->d_mats; sc.verts = ctx->d_verts; sc.tri_flags = ctx->d_flags; sc.normals = pt->d_normals;
+	sc.lds.sigma = pt->d_sigma; sc.lds.offset = pt->d_offset; sc.lds.prime = pt->d_prime; sc.lds.inv_prime = pt->d_inv_prime;
+	if(!pt->d_scene) Y4_CUDA(ctx, cudaMalloc(&pt->d_scene, sizeof(Y4PtScene)));
+	Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_scene, &sc, sizeof(Y4PtScene), cudaMemcpyHostToDevice, st));
+	// film (internal unless the caller installs buffers)
+	const size_t npx = (size_t) sc.width * sc.height;
+	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); pt->own_film_w = pt->own_film_rgba = nullptr;
+	Y4_CUDA(ctx, cudaMalloc(&pt->own_film_w, npx * sizeof(float)));
+	Y4_CUDA(ctx, cudaMalloc(&pt->own_film_rgba, npx * 4 * sizeof(float)));
+	Y4_CUDA(ctx, cudaMemsetAsync(pt->own_film_w, 0, npx * sizeof(float), st));
+	Y4_CUDA(ctx, cudaMemsetAsync(pt->own_film_rgba, 0, npx * 4 * sizeof(float), st));
+	pt->d_film_w = pt->own_film_w; pt->d_film_rgba = pt->own_film_rgba;
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	pt->params = *params;
+	pt->scene_set = true;
+	return Y4GPU_OK;
+}
+
+int y4gpu_pt_set_film_buffers(y4gpu_ctx *ctx, float *d_weights, float *d_rgba)
+{
+	if(!ctx) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4Pt *pt = ctx->pt;
+	if(!pt || !pt->scene_set) { ctx->err = "y4gpu_pt_set_film_buffers before y4gpu_pt_set_scene"; return Y4GPU_ERR_ARG; }
+	if(!d_weights != !d_rgba) return Y4GPU_ERR_ARG;
+	if(d_weights && (!pt_is_device_ptr(d_weights) || !pt_is_device_ptr(d_rgba))) { ctx->err = "film buffers must be device memory"; return Y4GPU_ERR_ARG; }
+	pt->d_film_w = d_weights ? d_weights : pt->own_film_w;
+	pt->d_film_rgba = d_rgba ? d_rgba : pt->own_film_rgba;
+	return Y4GPU_OK;
+}
+
+int y4gpu_pt_clear_film(y4gpu_ctx *ctx)
+{
+	if(!ctx) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4Pt *pt = ctx->pt;
+	if(!pt || !pt->scene_set) { ctx->err = "y4gpu_pt_clear_film before y4gpu_pt_set_scene"; return Y4GPU_ERR_ARG; }
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	const size_t npx = (size_t) pt->h_scene.width * pt->h_scene.height;
+	Y4_CUDA(ctx, cudaMemsetAsync(pt->d_film_w, 0, npx * sizeof(float), ctx->stream));
+	Y4_CUDA(ctx, cudaMemsetAsync(pt->d_film_rgba, 0, npx * 4 * sizeof(float), ctx->stream));
+	return Y4GPU_OK;
+}
+
+int y4gpu_pt_read_film(y4gpu_ctx *ctx, float *weights, float *rgba)
+{
+	if(!ctx || !weights || !rgba) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4Pt *pt = ctx->pt;
+	if(!pt || !pt->scene_set) { ctx->err = "y4gpu_pt_read_film before y4gpu_pt_set_scene"; return Y4GPU_ERR_ARG; }
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	const size_t npx = (size_t) pt->h_scene.width * pt->h_scene.height;
+	Y4_CUDA(ctx, cudaMemcpyAsync(weights, pt->d_film_w, npx * sizeof(float), cudaMemcpyDefault, ctx->stream));
+	Y4_CUDA(ctx, cudaMemcpyAsync(rgba, pt->d_film_rgba, npx * 4 * sizeof(float), cudaMemcpyDefault, ctx->stream));
+	Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return Y4GPU_OK;
+}
+
+int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out)
+{
+	if(!ctx || !out || !ctx->pt) return Y4GPU_ERR_ARG;
+	*out = ctx->pt->stats;
+	float ms = 0.f;
+	if(ctx->pt->ev1 && cudaEventQuery(ctx->pt->ev1) == cudaSuccess && cudaEventElapsedTime(&ms, ctx->pt->ev0, ctx->pt->ev1) == cudaSuccess) out->pass_ms = ms;
+	else cudaGetLastError();
+	return Y4GPU_OK;
+}
+
+} // extern "C"
+
+// ---- one AA pass (TiledIntegrator::renderPass) -------------------------------------------------------
+extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, int aa_pass_number,
+                                    const uint32_t *pixel_list, uint64_t n_pixels, int shard_index, int shard_count)
+{
+	if(!ctx || n_samples < 0 || shard_count < 1 || shard_index < 0 || shard_index >= shard_count) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4Pt *pt = ctx->pt;
+	if(!pt || !pt->scene_set) { ctx->err = "y4gpu_pt_render_pass before y4gpu_pt_set_scene"; return Y4GPU_ERR_ARG; }
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	cudaStream_t st = ctx->stream;
+	Y4PtScene &sc = pt->h_scene;
+	const uint64_t launches0 = ctx->stats.kernel_launches;
+	uint64_t own_launches = 0, rays_closest = 0, rays_shadow = 0;
+	// per-pass light sample multiplier (integrator_tiled.cc:189-191: multiplied once per additional pass)
+	float mult = 1.f;
+	for(int p = 0; p < aa_pass_number; ++p) mult *= pt->params.aa_light_sample_multiplier_factor > 0.f ? pt->params.aa_light_sample_multiplier_factor : 1.f;
+	if(mult != sc.aa_light_sample_multiplier)
+	{
+		sc.aa_light_sample_multiplier = mult;
+		pt->max_light_samples = 1;
+		for(int i = 0; i < sc.n_lights; ++i) { const int ns = y4_light_num_samples(sc, sc.lights[i]); if(ns > pt->max_light_samples) pt->max_light_samples = ns; }
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_scene, &sc, sizeof(Y4PtScene), cudaMemcpyHostToDevice, st));
+	}
+	const uint64_t n_pix = pixel_list ? n_pixels : (uint64_t) sc.width * sc.height;
+	const uint32_t ns_local = shard_index < n_samples ? (uint32_t) ((n_samples - shard_index + shard_count - 1) / shard_count) : 0u;
+	const uint64_t total = n_pix * ns_local;
+	Y4_CUDA(ctx, cudaEventRecord(pt->ev0, st));
+	const uint32_t *d_list = nullptr;
+	if(pixel_list && n_pixels)
+	{
+		if(pt_is_device_ptr(pixel_list)) d_list = pixel_list;
+		else
+		{
+			if(n_pixels > pt->pixel_list_cap)
+			{
+				cudaFree(pt->d_pixel_list); pt->d_pixel_list = nullptr; pt->pixel_list_cap = 0;
+				Y4_CUDA(ctx, cudaMalloc(&pt->d_pixel_list, n_pixels * sizeof(uint32_t)));
+				pt->pixel_list_cap = n_pixels;
+			}
+			Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_pixel_list, pixel_list, n_pixels * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+			d_list = pt->d_pixel_list;
+		}
+	}
+	uint32_t wave_size = pt->params.wave_size ? pt->params.wave_size : (1u << 21);
+	if(total < wave_size) wave_size = (uint32_t) (total ? total : 1);
+	{ const int rc = pt_alloc_wave(ctx, pt, wave_size); if(rc) return rc; }
+	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass_number;
+	const Y4PtScene *dsc = pt->d_scene;
+#define Y4_PT_LAUNCH(kernel, ...) do { kernel<<<grid, kPtThreads, 0, st>>>(__VA_ARGS__); ++own_launches; } while(0)
+#define Y4_PT_TRACE(kind, rays, count, hits) do { const int rc_ = y4_launch_trace(ctx, kind, false, rays, count, hits); if(rc_) return rc_; } while(0)
+	for(uint64_t first = 0; first < total; first += wave_size)
+	{
+		Y4PtWave W = pt->wave;
+		W.n = (uint32_t) ((total - first) < wave_size ? (total - first) : wave_size);
+		const int grid = pt_grid(ctx, W.n);
+		Y4_PT_LAUNCH(k_pt_fill, W, d_list, first, ns_local, shard_index, shard_count);
+		Y4_PT_LAUNCH(k_pt_gen, dsc, W, ps);
+		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.n, W.hit); rays_closest += W.n;
+		Y4_PT_LAUNCH(k_pt_primary, dsc, W);
+		for(int l = 0; l < sc.n_lights; ++l)
+		{
+			const int ns = y4_light_num_samples(sc, sc.lights[l]);
+			for(int k = 0; k < ns; ++k)
+			{
+				Y4_PT_LAUNCH(k_pt_direct, dsc, W, ps, 1, l, k);
+				Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, 2ull * W.n, W.shit); rays_shadow += 2ull * W.n;
+				Y4_PT_LAUNCH(k_pt_direct_resolve, dsc, W, 1, l, k);
+			}
+		}
+		for(int sub = 0; sub < sc.n_paths; ++sub)
+			for(int depth = 0; depth < sc.bounces; ++depth)
+			{
+				Y4_PT_LAUNCH(k_pt_bounce_sample, dsc, W, ps, depth, sub);
+				Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.n, W.hit); rays_closest += W.n;
+				Y4_PT_LAUNCH(k_pt_bounce_hit, dsc, W, ps, depth, sub);
+				if(sc.n_lights == 0) continue;
+				for(int k = 0; k < pt->max_light_samples; ++k)
+				{
+					Y4_PT_LAUNCH(k_pt_direct, dsc, W, ps, 0, -1, k);
+					Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, 2ull * W.n, W.shit); rays_shadow += 2ull * W.n;
+					Y4_PT_LAUNCH(k_pt_direct_resolve, dsc, W, 0, -1, k);
+				}
+			}
+		Y4_PT_LAUNCH(k_pt_splat, dsc, W, ps, pt->d_film_w, pt->d_film_rgba);
+		Y4_CUDA(ctx, cudaGetLastError());
+	}
+#undef Y4_PT_LAUNCH
+#undef Y4_PT_TRACE
+	Y4_CUDA(ctx, cudaEventRecord(pt->ev1, st));
+	ctx->stats.kernel_launches += own_launches;
+	pt->stats.samples = total;
+	pt->stats.rays_closest = rays_closest; pt->stats.rays_shadow = rays_shadow;
+	pt->stats.kernel_launches = ctx->stats.kernel_launches - launches0;
+	return Y4GPU_OK;
 }

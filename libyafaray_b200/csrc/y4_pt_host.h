@@ -1,0 +1,165 @@
+// Host-side derivation of the device scene description from the parameter-level C-ABI structs
+// (include/y4gpu.h), restating the reference constructors in plain fp32 with the reference's
+// operation order.  Included by y4_pt.cu (product) and by the CPU unit-test emulation.
+#pragma once
+#include "y4_pt_stages.cuh"
+#include "../../include/y4gpu.h"
+#include <cstring>
+
+namespace y4host {
+
+// ---- host-side restatement of the reference's derived scene state (plain fp32, reference order) ----
+struct HV { float x, y, z; };
+inline HV hv(const float *p) { return {p[0], p[1], p[2]}; }
+inline HV operator-(HV a, HV b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline HV operator+(HV a, HV b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline HV operator*(float f, HV v) { return {f * v.x, f * v.y, f * v.z}; }
+inline HV operator*(HV v, float f) { return {f * v.x, f * v.y, f * v.z}; }
+inline HV operator^(HV a, HV b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline float lensqr(HV v) { return v.x * v.x + v.y * v.y + v.z * v.z; }
+inline HV normalized(HV v)
+{
+	float len = lensqr(v);
+	if(len != 0.f) { len = 1.f / sqrtf(len); v.x *= len; v.y *= len; v.z *= len; }
+	return v;
+}
+inline V3 tov(HV v) { return v3(v.x, v.y, v.z); }
+
+// Camera::Camera + PerspectiveCamera::PerspectiveCamera/setAxis (camera.cc:51-71, camera_perspective.cc:28-69)
+inline Y4PtCamera derive_camera(const y4gpu_pt_camera &c)
+{
+	Y4PtCamera o;
+	const HV position = hv(c.from), look = hv(c.to), up = hv(c.up);
+	const float aspect_ratio = c.aspect_ratio * (float) c.resy / (float) c.resx;
+	HV cam_y = up - position;
+	HV cam_z = look - position;
+	HV cam_x = cam_z ^ cam_y;
+	cam_y = cam_z ^ cam_x;
+	cam_x = normalized(cam_x); cam_y = normalized(cam_y); cam_z = normalized(cam_z);
+	const HV near_p = position + cam_z * c.near_clip, far_p = position + cam_z * c.far_clip;
+	HV vright = cam_x;
+	HV vup = aspect_ratio * cam_y;
+	const HV vto = (cam_z * c.focal) - 0.5f * (vup + vright);
+	vup = {vup.x / (float) c.resy, vup.y / (float) c.resy, vup.z / (float) c.resy};
+	vright = {vright.x / (float) c.resx, vright.y / (float) c.resx, vright.z / (float) c.resx};
+	o.pos = tov(position); o.vright = tov(vright); o.vup = tov(vup); o.vto = tov(vto);
+	o.near_p = tov(near_p); o.near_n = tov(cam_z); o.far_p = tov(far_p); o.far_n = tov(cam_z);
+	o.resx = c.resx; o.resy = c.resy;
+	return o;
+}
+
+// ShinyDiffuseMaterial ctor + config() (material_shiny_diffuse.cc:29-82), LightMaterial (material_simple.cc:36-70)
+inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
+{
+	Y4PtMaterial o;
+	memset(&o, 0, sizeof(o));
+	o.type = m.type;
+	o.receive_shadows = m.receive_shadows; o.flat_material = m.flat_material; o.double_sided = m.double_sided;
+	if(m.type == Y4GPU_MAT_LIGHT)
+	{
+		const float power = (float) (double) m.emit;       // col * static_cast<float>(power)
+		o.color = c3(power * m.color[0], power * m.color[1], power * m.color[2]);
+		o.bsdf_flags = Y4_BSDF_EMIT;
+		return o;
+	}
+	o.color = c3(m.color[0], m.color[1], m.color[2]);
+	o.emit = c3(m.emit * m.color[0], m.emit * m.color[1], m.emit * m.color[2]);
+	if(m.emit > 0.f) o.bsdf_flags |= Y4_BSDF_EMIT;
+	const float acc = 1.f;                                    // no mirror / transparency / translucency components
+	if(m.diffuse_reflect * acc > 0.00001f)
+	{
+		o.is_diffuse = 1; o.diffuse_strength = m.diffuse_reflect;
+		o.bsdf_flags |= Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
+	}
+	if(m.oren_nayar)
+	{
+		const double sigma = (double) m.sigma, s2 = sigma * sigma;     // initOrenNayar (:150-156)
+		o.oren_a = (float) (1.0 - 0.5 * (s2 / (s2 + 0.33)));
+		o.oren_b = (float) (0.45 * s2 / (s2 + 0.09));
+		o.oren_nayar = 1;
+	}
+	return o;
+}
+
+// PointLight ctor (light_point.cc:29-36), AreaLight ctor (light_area.cc:33-52)
+inline Y4PtLight derive_light(const y4gpu_pt_light &l)
+{
+	Y4PtLight o;
+	memset(&o, 0, sizeof(o));
+	o.type = l.type; o.samples = l.samples; o.cast_shadows = l.cast_shadows;
+	o.pos = v3(l.from[0], l.from[1], l.from[2]);
+	if(l.type == Y4GPU_LIGHT_POINT)
+	{
+		o.color = c3(l.power * l.color[0], l.power * l.color[1], l.power * l.color[2]);
+		return o;
+	}
+	const HV corner = hv(l.from), to_x = hv(l.point1) - corner, to_y = hv(l.point2) - corner;
+	HV fnormal = to_y ^ to_x;
+	const float pi_f = (float) 3.14159265358979323846264338327950288L;
+	o.color = c3(pi_f * (l.power * l.color[0]), pi_f * (l.power * l.color[1]), pi_f * (l.power * l.color[2]));   // col * inte * num_pi
+	// area_ = fnormal_.normLen(): normalises fnormal_ and returns its former length (vector.h)
+	float len = lensqr(fnormal);
+	float area = 0.f;
+	if(len != 0.f)
+	{
+		area = sqrtf(len);
+		const float inv = 1.f / area;
+		fnormal = {fnormal.x * inv, fnormal.y * inv, fnormal.z * inv};
+	}
+	o.area = area; o.inv_area = (float) (1.0 / (double) area);
+	o.fnormal = tov(fnormal);
+	o.normal = v3(-fnormal.x, -fnormal.y, -fnormal.z);
+	o.to_x = tov(to_x); o.to_y = tov(to_y);
+	o.c2 = tov(corner + to_x); o.c3 = tov(corner + (to_x + to_y)); o.c4 = tov(corner + to_y);
+	return o;
+}
+
+// ImageFilm ctor: filter table, filter width, table scale (imagefilm.cc:129-173, math/filter.h:34-90)
+inline bool derive_film(const y4gpu_pt_params &p, Y4PtScene &sc)
+{
+	double filterw = (double) p.aa_pixelwidth * 0.5;          // filterw_(filter_size * 0.5)
+	float filterw_f = (float) filterw;                        // float filterw_ member
+	int kind = p.filter_type;
+	if(kind == Y4GPU_FILTER_MITCHELL) filterw_f *= 2.6f;
+	else if(kind == Y4GPU_FILTER_GAUSS) filterw_f *= 2.f;
+	else if(kind != Y4GPU_FILTER_LANCZOS) kind = Y4GPU_FILTER_BOX;
+	const int max_filter_size = 8;
+	filterw_f = fminf(fmaxf(0.501f, filterw_f), 0.5f * max_filter_size);
+	const float scale = 1.f / (float) Y4_FILTER_TABLE;
+	for(int y = 0; y < Y4_FILTER_TABLE; ++y)
+		for(int x = 0; x < Y4_FILTER_TABLE; ++x)
+		{
+			const float dx = (x + .5f) * scale, dy = (y + .5f) * scale;
+			float v = 1.f;
+			if(kind == Y4GPU_FILTER_GAUSS)
+			{
+				const float r_2 = dx * dx + dy * dy;
+				v = fmaxf(0.f, y4_fast_exp(-6 * r_2) - 0.00247875f);
+			}
+			else if(kind == Y4GPU_FILTER_MITCHELL)
+			{
+				const float xx = 2.f * sqrtf(dx * dx + dy * dy);
+				if(xx >= 2.f) v = 0.f;
+				else if(xx >= 1.f) v = xx * (xx * (xx * -0.38888889f + 2.0f) - 3.33333333f) + 1.77777778f;
+				else v = xx * xx * (1.16666666f * xx - 2.0f) + 0.88888889f;
+			}
+			else if(kind == Y4GPU_FILTER_LANCZOS)
+			{
+				const float xx = sqrtf(dx * dx + dy * dy);
+				if(xx == 0.f) v = 1.f;
+				else if(-2 < xx && xx < 2)
+				{
+					const float a = (float) (Y4_PI * (Y4_WIDE) xx), b = (float) (Y4_PI_2 * (Y4_WIDE) xx);
+					v = (y4_fast_sin(a) * y4_fast_sin(b)) / (a * b);
+				}
+				else v = 0.f;
+			}
+			sc.filter_table[y * Y4_FILTER_TABLE + x] = v;
+		}
+	sc.filterw = (double) filterw_f;
+	sc.table_scale = (double) (float) (0.9999 * Y4_FILTER_TABLE / (double) filterw_f);     // float table_scale_ member
+	return true;
+}
+
+} // namespace y4host
+using namespace y4host;

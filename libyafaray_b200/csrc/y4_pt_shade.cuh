@@ -1,0 +1,249 @@
+// Per-vertex shading logic of the wavefront path tracer: surface set-up, the supported
+// materials (shinydiffusemat without mirror/transparency/translucency/nodes, light_mat), the
+// supported lights (pointlight, arealight) and one direct-light sample with MIS.  Restated from
+// the reference operation for operation (never-contracted fp32, see y4_common.cuh):
+//   TrianglePrimitive::getSurface              src/geometry/primitive/primitive_triangle.cc:97-176
+//   ShinyDiffuseMaterial::sample/eval/pdf/emit src/material/material_shiny_diffuse.cc:197-385
+//   ShinyDiffuseMaterial::orenNayar            src/material/material_shiny_diffuse.cc:161-195
+//   LightMaterial::sample/emit                 src/material/material_simple.cc:41-58
+//   PointLight::illuminate                     src/light/light_point.cc:38-57
+//   AreaLight::illumSample/intersect           src/light/light_area.cc:66-96,117-151
+//   MonteCarloIntegrator::diracLight / areaLightSampleLight / areaLightSampleMaterial
+//                                              src/integrator/surface/integrator_montecarlo.cc:80-383
+#pragma once
+#include "y4_pt_types.cuh"
+
+// ---- surface ---------------------------------------------------------------------------------
+Y4_HD Y4Surf y4_surface(const Y4PtScene &sc, const V3 ray_o, const V3 ray_d, float t, float bu, float bv, int32_t prim)
+{
+	Y4Surf s;
+	const float *v = sc.verts + 9ull * (uint32_t) prim;
+	const V3 a = v3(v[0], v[1], v[2]), b = v3(v[3], v[4], v[5]), c = v3(v[6], v[7], v[8]);
+	s.ng = xnormalize(xcross(xsub3(b, a), xsub3(c, a)));            // calculateNormal, :92-95
+	if(sc.normals)
+	{
+		const float *nn = sc.normals + 9ull * (uint32_t) prim;
+		const float u = xsub(xsub(1.f, bu), bv);                      // barycentric_u_ = 1 - u - v (:66)
+		const V3 n0 = v3(nn[0], nn[1], nn[2]), n1 = v3(nn[3], nn[4], nn[5]), n2 = v3(nn[6], nn[7], nn[8]);
+		s.n = xnormalize(xadd3(xadd3(xscale(n0, u), xscale(n1, bu)), xscale(n2, bv)));
+	}
+	else s.n = s.ng;
+	s.p = xadd3(ray_o, xscale(ray_d, t));                            // ray.from_ + t * ray.dir_ (accelerator.cc:62)
+	y4_coords_system(s.n, s.nu, s.nv);
+	s.mat = sc.tri_flags ? (sc.tri_flags[prim] >> Y4_TRI_MAT_SHIFT) : 0u;
+	if(s.mat >= (uint32_t) sc.n_mats) s.mat = 0u;
+	return s;
+}
+Y4_HD V3 y4_face_forward(const V3 ng, const V3 n, const V3 incoming) { return xdot(ng, incoming) < 0.f ? xneg(n) : n; }
+
+// ---- materials ---------------------------------------------------------------------------------
+Y4_HD float y4_oren_nayar(const Y4PtMaterial &m, const V3 wi, const V3 wo, const V3 n)
+{
+	const float cos_ti = fmaxf(-1.f, fminf(1.f, xdot(n, wi)));
+	const float cos_to = fmaxf(-1.f, fminf(1.f, xdot(n, wo)));
+	float maxcos_f = 0.f;
+	if(cos_ti < 0.9999f && cos_to < 0.9999f)
+	{
+		const V3 v1 = xnormalize(xsub3(wi, xscale(n, cos_ti)));
+		const V3 v2 = xnormalize(xsub3(wo, xscale(n, cos_to)));
+		maxcos_f = fmaxf(0.f, xdot(v1, v2));
+	}
+	float sin_alpha, tan_beta;
+	if(cos_to >= cos_ti)
+	{
+		sin_alpha = xsqrt(xsub(1.f, xmul(cos_ti, cos_ti)));
+		tan_beta = xdiv(xsqrt(xsub(1.f, xmul(cos_to, cos_to))), (cos_to == 0.f) ? 1e-8f : cos_to);
+	}
+	else
+	{
+		sin_alpha = xsqrt(xsub(1.f, xmul(cos_to, cos_to)));
+		tan_beta = xdiv(xsqrt(xsub(1.f, xmul(cos_ti, cos_ti))), (cos_ti == 0.f) ? 1e-8f : cos_ti);
+	}
+	return fminf(1.f, fmaxf(0.f, xadd(m.oren_a, xmul(xmul(xmul(m.oren_b, maxcos_f), sin_alpha), tan_beta))));
+}
+
+// Material::sample -> returns scolor; wi, w, pdf, sampled (false == BsdfFlags::None) are outputs.
+// `w` is left untouched when nothing is sampled (the reference leaves its out-parameter alone too).
+Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, float s1, float s2, uint32_t flags,
+                       V3 &wi, float &w, float &pdf, bool &sampled)
+{
+	sampled = false; pdf = 0.f;
+	if(m.type == Y4GPU_MAT_LIGHT) { w = 0.f; return c3f(0.f); }
+	const float cos_ng_wo = xdot(sp.ng, wo);
+	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
+	const uint32_t cflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
+	float sum = 0.f, width = 0.f, val = 0.f;
+	int n_match = 0;
+	if(m.is_diffuse && (flags & cflags) == cflags) { width = m.diffuse_strength; sum = xadd(sum, width); val = sum; n_match = 1; }
+	if(!n_match || sum < 0.00001f) return c3f(1.f);
+	const float inv_sum = xdiv(1.f, sum);
+	val = xmul(val, inv_sum); width = xmul(width, inv_sum);
+	(void) val;                                                    // single component: pick == 0 either way
+	const float s_1 = xdiv(s1, width);
+	wi = y4_cos_hemisphere(n, sp.nu, sp.nv, s_1, s2);
+	C3 scolor = c3f(0.f);
+	if(xmul(cos_ng_wo, xdot(sp.ng, wi)) > 0.f) scolor = cscale(m.color, m.diffuse_strength);   // accum_c[3] * colour
+	if(m.oren_nayar) scolor = cscale(scolor, y4_oren_nayar(m, wo, wi, n));
+	pdf = xmul(fabsf(xdot(wi, n)), width);
+	sampled = true;
+	w = xdiv(fabsf(xdot(wi, sp.n)), xadd(xmul(pdf, 0.99f), 0.01f));
+	w = xadd(xmul(w, 1.f), xmul(1.f, xsub(1.f, 1.f)));             // alpha == 1 for opaque materials
+	return scolor;
+}
+
+Y4_HD C3 y4_mat_eval(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, const V3 wl)
+{
+	if(m.type == Y4GPU_MAT_LIGHT || !m.is_diffuse) return c3f(0.f);     // Material::eval default / no Diffuse flag
+	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
+	if(xdot(n, wl) < 0.f && !m.flat_material) return c3f(0.f);
+	float m_d = xmul(xmul(1.f, xsub(1.f, 0.f)), m.diffuse_strength);
+	if(m.oren_nayar) m_d = xmul(m_d, y4_oren_nayar(m, wo, wl, n));
+	return cscale(m.color, m_d);
+}
+
+Y4_HD float y4_mat_pdf(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, const V3 wi)
+{
+	if(m.type == Y4GPU_MAT_LIGHT || !m.is_diffuse) return 0.f;
+	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
+	const float width = m.diffuse_strength;
+	const float sum = xadd(0.f, width);
+	const float pdf = xadd(0.f, xmul(fabsf(xdot(wi, n)), width));
+	if(sum < 0.00001f) return 0.f;
+	return xdiv(pdf, sum);
+}
+
+Y4_HD C3 y4_mat_emit(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo)
+{
+	if(m.type == Y4GPU_MAT_LIGHT)
+	{
+		if(m.double_sided) return m.color;
+		return xdot(wo, sp.n) > 0.f ? m.color : c3f(0.f);
+	}
+	return m.emit;
+}
+
+// ---- one direct-light sample -------------------------------------------------------------------
+// Produces up to two shadow rays with the radiance each carries if unoccluded:
+//   slot 0: the light sample (dirac light, or areaLightSampleLight's i-th sample)
+//   slot 1: the BSDF sample that completes MIS for intersectable lights (areaLightSampleMaterial)
+// Contributions are per-sample terms; the caller sums them over the light's samples and applies
+// inv_num_samples exactly like the reference (col * inv_num_samples per sub-estimator).
+struct Y4DirectOut
+{
+	Y4Ray ray[2];
+	C3 contrib[2];
+	bool valid[2];
+};
+
+Y4_HD Y4Ray y4_null_ray() { Y4Ray r; r.ox = r.oy = r.oz = 0.f; r.tmin = 0.f; r.dx = 0.f; r.dy = 0.f; r.dz = 1.f; r.tmax = 0.f; return r; }
+Y4_HD Y4Ray y4_mk_ray(const V3 o, float tmin, const V3 d, float tmax)
+{
+	Y4Ray r; r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmin = tmin; r.dx = d.x; r.dy = d.y; r.dz = d.z; r.tmax = tmax; return r;
+}
+
+Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo,
+                            float s1, float s2, Y4DirectOut &out)
+{
+	out.valid[0] = out.valid[1] = false;
+	out.contrib[0] = out.contrib[1] = c3f(0.f);
+	out.ray[0] = out.ray[1] = y4_null_ray();
+	const float plen = xlen(sp.p);
+	const float tmin_shadow = sc.shadow_bias_auto ? xmul(sc.shadow_bias, fmaxf(1.f, plen)) : sc.shadow_bias;
+	if(L.type == Y4GPU_LIGHT_POINT)
+	{
+		// PointLight::illuminate + MonteCarloIntegrator::diracLight
+		V3 ldir = xsub3(L.pos, sp.p);
+		const float dist_sqr = xadd(xadd(xmul(ldir.x, ldir.x), xmul(ldir.y, ldir.y)), xmul(ldir.z, ldir.z));
+		const float dist = xsqrt(dist_sqr);
+		if(dist == 0.f) return;
+		const float idist_sqr = xdiv(1.f, dist_sqr);
+		ldir = xscale(ldir, xdiv(1.f, dist));
+		const C3 lcol = cscale(L.color, idist_sqr);
+		const float angle = m.flat_material ? 1.f : fabsf(xdot(sp.n, ldir));
+		const C3 surf = y4_mat_eval(m, sp, wo, ldir);
+		out.contrib[0] = cscale(cscale(cmul(surf, lcol), angle), 1.f);      // surf_col * lcol * angle * transmit_col(1)
+		out.ray[0] = y4_mk_ray(sp.p, tmin_shadow, ldir, dist);
+		out.valid[0] = true;
+		return;
+	}
+	// ---- AreaLight::illumSample + areaLightSampleLight ----
+	{
+		const V3 p = xadd3(xadd3(L.pos, xscale(L.to_x, s1)), xscale(L.to_y, s2));
+		V3 ldir = xsub3(p, sp.p);
+		const float dist_sqr = xdot(ldir, ldir);
+		const float dist = xsqrt(dist_sqr);
+		if(dist > 0.f)
+		{
+			ldir = xscale(ldir, xdiv(1.f, dist));
+			const float cos_angle = xdot(ldir, L.fnormal);
+			if(cos_angle > 0.f)
+			{
+				// dist_sqr * math::num_pi / (area_ * cos_angle): num_pi is long double -> wide product and quotient, one rounding to float
+				const float ls_pdf = (float) (xdmul((Y4_WIDE) dist_sqr, Y4_PI) / (Y4_WIDE) xmul(L.area, cos_angle));
+				if(ls_pdf > 1e-6f)
+				{
+					const C3 surf = y4_mat_eval(m, sp, wo, ldir);
+					const float angle = m.flat_material ? 1.f : fabsf(xdot(sp.n, ldir));
+					float w = 1.f;
+					const float m_pdf = y4_mat_pdf(m, sp, wo, ldir);
+					if(m_pdf > 1e-6f)
+					{
+						const float l2 = xmul(ls_pdf, ls_pdf), m2 = xmul(m_pdf, m_pdf);
+						w = xdiv(l2, xadd(l2, m2));
+					}
+					out.contrib[0] = cdiv(cscale(cscale(cmul(surf, L.color), angle), w), ls_pdf);
+					out.ray[0] = y4_mk_ray(sp.p, tmin_shadow, ldir, dist);
+					out.valid[0] = true;
+				}
+			}
+		}
+	}
+	// ---- areaLightSampleMaterial + AreaLight::intersect ----
+	{
+		const float tmin_b = sc.ray_min_dist_auto ? xmul(sc.ray_min_dist, fmaxf(1.f, plen)) : sc.ray_min_dist;
+		V3 wi = v3(0.f, 0.f, 0.f);
+		float W = 0.f, s_pdf = 0.f; bool sampled;
+		const uint32_t fl = Y4_BSDF_GLOSSY | Y4_BSDF_DIFFUSE | Y4_BSDF_DISPERSIVE | Y4_BSDF_REFLECT | Y4_BSDF_TRANSMIT;
+		const C3 surf = y4_mat_sample(m, sp, wo, s1, s2, fl, wi, W, s_pdf, sampled);
+		if(s_pdf > 1e-6f)
+		{
+			const float cos_angle = xdot(wi, L.fnormal);
+			if(cos_angle > 0.f)
+			{
+				float t = 0.f; bool hit = false;
+				// triIntersect(corner, c2, c3) then (corner, c3, c4), light_area.cc:117-134 (ray.from_ == sp.p, no tmin)
+				for(int k = 0; k < 2 && !hit; ++k)
+				{
+					const V3 a = L.pos, b = k ? L.c3 : L.c2, c = k ? L.c4 : L.c3;
+					const V3 e1 = xsub3(b, a), e2 = xsub3(c, a);
+					const V3 pvec = xcross(wi, e2);
+					const float det = xdot(e1, pvec);
+					if(det == 0.f) continue;
+					const float inv_det = xdiv(1.f, det);
+					const V3 tvec = xsub3(sp.p, a);
+					const float u = xmul(xdot(tvec, pvec), inv_det);
+					if(u < 0.f || u > 1.f) continue;
+					const V3 qvec = xcross(tvec, e1);
+					const float v = xmul(xdot(wi, qvec), inv_det);
+					if((v < 0.f) || (xadd(u, v) > 1.f)) continue;
+					t = xmul(xdot(e2, qvec), inv_det);
+					hit = true;
+				}
+				if(hit && t > 1.0e-10f)
+				{
+					// 1.f / (t * t) * area_ * cos_angle * math::div_1_by_pi (last factor long double)
+					const float ipdf = (float) xdmul((Y4_WIDE) xmul(xmul(xdiv(1.f, xmul(t, t)), L.area), cos_angle), Y4_1_PI);
+					if(ipdf > 1e-6f)
+					{
+						const float l_pdf = xdiv(1.f, ipdf);
+						const float l2 = xmul(l_pdf, l_pdf), m2 = xmul(s_pdf, s_pdf);
+						const float w = xdiv(m2, xadd(l2, m2));
+						out.contrib[1] = cscale(cscale(cmul(surf, L.color), w), W);
+						out.ray[1] = y4_mk_ray(sp.p, tmin_b, wi, t);
+						out.valid[1] = true;
+					}
+				}
+			}
+		}
+	}
+}

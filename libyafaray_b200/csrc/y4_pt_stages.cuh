@@ -1,0 +1,352 @@
+// Wavefront stages of the path tracer, one call per path (Y4_HD: the kernels in y4_pt.cu and the
+// CPU unit-test emulation run the same code).  Control flow restated from
+//   TiledIntegrator::renderTile        src/integrator/surface/integrator_tiled.cc:269-408
+//   PerspectiveCamera::shootRay        src/camera/camera_perspective.cc:128-146
+//   PathIntegrator::integrate          src/integrator/surface/integrator_path_tracer.cc:120-290
+//   estimateAllDirectLight / estimateOneDirectLight / doLightEstimation
+//                                      src/integrator/surface/integrator_montecarlo.cc:54-78,385-408
+//   ImageFilm::addSample               src/render/imagefilm.cc:680-733
+#pragma once
+#include "y4_pt_shade.cuh"
+
+struct Y4PtWave
+{
+	uint32_t n;            // pixel-samples in this wave
+	uint32_t *pix;         // (y - cy0) * width + (x - cx0)
+	uint32_t *samp;        // sample loop index inside the pass (0 .. n_samples-1)
+	uint32_t *flags;       // Y4_PF_*
+	uint32_t *lnum;        // light chosen by estimateOneDirectLight for the current vertex
+	float *col;            // [n*4] radiance of the pixel-sample (rgb) + alpha
+	float *pcol;           // [n*4] path_col (sum over the path_samples sub-paths)
+	float *thr;            // [n*4] throughput
+	float *lcol;           // [n*4] emitted light picked up at the current vertex
+	float *acc_a, *acc_b;  // [n*4] per-light sums of the light-sample / BSDF-sample estimators
+	Y4Ray *ray; Y4Hit *hit; Y4Hit *hit0;
+	Y4Ray *sray;           // [2n] shadow rays: slot 0 at [i], slot 1 at [n + i]
+	Y4Hit *shit;           // [2n]
+	float *scontrib;       // [2n*4]
+};
+
+struct Y4PtPass
+{
+	int n_samples;         // samples per pixel in this pass (all shards together)
+	uint32_t pass_offs;    // offset + ImageFilm::getBaseSamplingOffset()
+	int aa_pass;
+};
+
+Y4_HD C3 ld3(const float *p, uint32_t i) { return c3(p[4ull * i], p[4ull * i + 1], p[4ull * i + 2]); }
+Y4_HD void st3(float *p, uint32_t i, C3 c) { p[4ull * i] = c.r; p[4ull * i + 1] = c.g; p[4ull * i + 2] = c.b; }
+
+struct Y4PixelSampling { int x, y; uint32_t offset; uint32_t sample; float dx, dy; };   // PixelSamplingData + jitter
+
+Y4_HD Y4PixelSampling y4_pixel_sampling(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp)
+{
+	Y4PixelSampling r;
+	r.x = sc.cx0 + (int) (pix % (uint32_t) sc.width);
+	r.y = sc.cy0 + (int) (pix / (uint32_t) sc.width);
+	r.offset = y4_fnv32a((uint32_t) r.y * y4_fnv32a((uint32_t) r.x));
+	r.sample = ps.pass_offs + samp;
+	r.dx = 0.5f; r.dy = 0.5f;
+	if(sc.aa_passes > 1)
+	{
+		r.dx = y4_ri_vdc(r.sample, r.offset);
+		r.dy = y4_ri_s(r.sample, r.offset);
+	}
+	else if(ps.n_samples > 1)
+	{
+		const float d_1 = xdiv(1.f, (float) ps.n_samples);
+		r.dx = xmul(xadd(0.5f, (float) (int) samp), d_1);
+		r.dy = y4_ri_lp(samp + r.offset, 0u);
+	}
+	return r;
+}
+
+Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py)
+{
+	V3 d = xadd3(xadd3(xscale(cam.vright, px), xscale(cam.vup, py)), cam.vto);
+	d = xnormalize(d);
+	// Plane::rayIntersection: n * (p - from) / (dir * n)
+	const float tmin = xdiv(xdot(cam.near_n, xsub3(cam.near_p, cam.pos)), xdot(d, cam.near_n));
+	const float tmax = xdiv(xdot(cam.far_n, xsub3(cam.far_p, cam.pos)), xdot(d, cam.far_n));
+	return y4_mk_ray(cam.pos, tmin, d, tmax);
+}
+
+// ---- stage: camera rays ------------------------------------------------------------------------
+Y4_HD void y4_pt_gen(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
+{
+	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+	W.ray[i] = y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy));
+	W.flags[i] = 0u;
+}
+Y4_HD Y4Ray y4_primary_ray(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
+{
+	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+	return y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy));
+}
+
+// ---- stage: camera-ray hit (integrate(), :126-171 up to the path loop) ---------------------------
+Y4_HD void y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i)
+{
+	const Y4Hit h = W.hit[i];
+	const Y4Ray r = W.ray[i];
+	W.hit0[i] = h;
+	st3(W.pcol, i, c3f(0.f)); st3(W.acc_a, i, c3f(0.f)); st3(W.acc_b, i, c3f(0.f)); st3(W.lcol, i, c3f(0.f)); st3(W.thr, i, c3f(0.f));
+	if(h.prim < 0)
+	{
+		const bool transp = sc.transp_background != 0;      // ray_level == 0
+		st3(W.col, i, transp ? c3f(0.f) : sc.background);
+		W.col[4ull * i + 3] = transp ? 0.f : 1.f;
+		W.flags[i] = 0u;
+		return;
+	}
+	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
+	const Y4Surf sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
+	const Y4PtMaterial m = sc.mats[sp.mat];
+	const V3 wo = xneg(d);
+	C3 col = c3f(0.f);
+	if(m.bsdf_flags & Y4_BSDF_EMIT) col = cadd(col, y4_mat_emit(m, sp, wo));
+	st3(W.col, i, col);
+	W.col[4ull * i + 3] = 1.f;                                // recursiveRaytrace: alpha_count == 0 -> 1
+	uint32_t f = Y4_PF_HIT0;
+	if(m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
+	const uint32_t path_flags = sc.no_recursive ? (uint32_t) Y4_BSDF_ALL : (uint32_t) Y4_BSDF_DIFFUSE;
+	if(m.bsdf_flags & path_flags) f |= Y4_PF_PATHS;
+	W.flags[i] = f;
+}
+
+// number of samples doLightEstimation takes from light L (integrator_montecarlo.cc:396)
+Y4_HD int y4_light_num_samples(const Y4PtScene &sc, const Y4PtLight &L)
+{
+	if(L.type == Y4GPU_LIGHT_POINT) return 1;
+	return (int) ceilf(xmul((float) L.samples, sc.aa_light_sample_multiplier));
+}
+
+// ---- stage: k-th sample of one light at the current vertex ---------------------------------------
+// all_lights: vertex = camera hit (estimateAllDirectLight, light index given);
+// otherwise : vertex = current path vertex, light = W.lnum[i] (estimateOneDirectLight).
+Y4_HD void y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, bool all_lights, int light, int k)
+{
+	const uint32_t n = W.n;
+	W.sray[i] = y4_null_ray(); W.sray[n + i] = y4_null_ray();
+	st3(W.scontrib, i, c3f(0.f)); st3(W.scontrib, n + i, c3f(0.f));
+	const uint32_t f = W.flags[i];
+	if(!(f & Y4_PF_DIRECT) || (!all_lights && !(f & Y4_PF_ALIVE))) return;
+	const int l = all_lights ? light : (int) W.lnum[i];
+	const Y4PtLight &L = sc.lights[l];
+	const int num_samples = y4_light_num_samples(sc, L);
+	if(k >= num_samples) return;
+	const Y4Ray r = all_lights ? y4_primary_ray(sc, W, ps, i) : W.ray[i];
+	const Y4Hit h = all_lights ? W.hit0[i] : W.hit[i];
+	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
+	const Y4Surf sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
+	const Y4PtMaterial m = sc.mats[sp.mat];
+	const V3 wo = xneg(d);
+	float s1 = 0.f, s2 = 0.f;
+	if(L.type != Y4GPU_LIGHT_POINT)
+	{
+		const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+		const uint32_t offs = (uint32_t) num_samples * s.sample + s.offset + (uint32_t) l * 4567u;
+		Y4Halton h2 = y4_halton_start(2u, offs - 1u), h3 = y4_halton_start(3u, offs - 1u);
+		for(int q = 0; q <= k; ++q) { s1 = y4_halton_next(h2); s2 = y4_halton_next(h3); }
+	}
+	Y4DirectOut out;
+	y4_direct_sample(sc, L, m, sp, wo, s1, s2, out);
+	const bool cast = L.cast_shadows && m.receive_shadows;
+	for(int q = 0; q < 2; ++q)
+	{
+		if(!out.valid[q]) continue;
+		if(cast) W.sray[q * n + i] = out.ray[q];
+		st3(W.scontrib, q * n + i, out.contrib[q]);
+	}
+}
+
+// ---- stage: fold the shadow-ray results of sample k into the light's estimators ------------------
+Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, bool all_lights, int light, int k)
+{
+	const uint32_t n = W.n;
+	const uint32_t f = W.flags[i];
+	if(!(f & Y4_PF_DIRECT) || (!all_lights && !(f & Y4_PF_ALIVE))) return;
+	const int l = all_lights ? light : (int) W.lnum[i];
+	const Y4PtLight &L = sc.lights[l];
+	const int num_samples = y4_light_num_samples(sc, L);
+	if(k >= num_samples) return;
+	C3 a = ld3(W.acc_a, i), b = ld3(W.acc_b, i);
+	if(W.shit[i].prim < 0) a = cadd(a, ld3(W.scontrib, i));
+	if(W.shit[n + i].prim < 0) b = cadd(b, ld3(W.scontrib, n + i));
+	if(k < num_samples - 1) { st3(W.acc_a, i, a); st3(W.acc_b, i, b); return; }
+	// last sample of this light: doLightEstimation's result
+	C3 dl = c3f(0.f);
+	if(L.type == Y4GPU_LIGHT_POINT) dl = cadd(dl, a);
+	else
+	{
+		const float inv = xdiv(1.f, (float) num_samples);
+		dl = cadd(dl, cscale(a, inv));
+		dl = cadd(dl, cscale(b, inv));
+	}
+	st3(W.acc_a, i, c3f(0.f)); st3(W.acc_b, i, c3f(0.f));
+	if(all_lights) st3(W.col, i, cadd(ld3(W.col, i), dl));                     // estimateAllDirectLight: col += ...
+	else
+	{
+		// estimateOneDirectLight: ... * num_lights; then "lcol += col_emit" (first vertex) and path_col += lcol * throughput
+		C3 lcol = cscale(dl, (float) sc.n_lights);
+		lcol = cadd(lcol, ld3(W.lcol, i));
+		st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, ld3(W.thr, i))));
+		st3(W.lcol, i, c3f(0.f));
+		W.flags[i] = f & ~(uint32_t) Y4_PF_DIRECT;
+	}
+}
+
+// ---- stage: BSDF sample that extends sub-path `sub` at bounce `depth` (integrate(), :163-231) ------
+Y4_HD void y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub)
+{
+	uint32_t f = W.flags[i];
+	if(depth == 0)
+	{
+		f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIFF1 | Y4_PF_DIRECT);
+		W.flags[i] = f;
+		if(!(f & Y4_PF_PATHS)) { W.ray[i] = y4_null_ray(); return; }
+	}
+	else if(!(f & Y4_PF_ALIVE)) { W.ray[i] = y4_null_ray(); return; }
+	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+	const uint32_t offs = (uint32_t) sc.n_paths * s.sample + s.offset + (uint32_t) sub;
+	const Y4Ray r = depth == 0 ? y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy)) : W.ray[i];
+	const Y4Hit h = depth == 0 ? W.hit0[i] : W.hit[i];
+	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
+	const Y4Surf sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
+	const Y4PtMaterial m = sc.mats[sp.mat];
+	const V3 pwo = xneg(d);
+	float s1, s2; uint32_t sflags;
+	if(depth == 0)
+	{
+		s1 = y4_ri_vdc(offs, 0u);
+		s2 = (float) y4_lds(sc.lds, 2, offs);
+		sflags = (sc.no_recursive ? (uint32_t) Y4_BSDF_ALL : (uint32_t) Y4_BSDF_DIFFUSE) | Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT | Y4_BSDF_TRANSMIT;
+	}
+	else
+	{
+		s1 = (float) y4_lds(sc.lds, 4 * depth + 3, offs);
+		s2 = (float) y4_lds(sc.lds, 4 * depth + 4, offs);
+		sflags = Y4_BSDF_ALL;
+	}
+	V3 wi = v3(0.f, 0.f, 1.f);
+	float w = 0.f, pdf; bool sampled;
+	C3 scol = y4_mat_sample(m, sp, pwo, s1, s2, sflags, wi, w, pdf, sampled);
+	scol = cscale(scol, w);
+	if(depth == 0) st3(W.thr, i, scol);
+	else
+	{
+		if(cblack(scol)) { W.flags[i] = f & ~(uint32_t) Y4_PF_ALIVE; W.ray[i] = y4_null_ray(); return; }
+		st3(W.thr, i, cmul(ld3(W.thr, i), scol));
+	}
+	if(!sampled) { W.flags[i] = f & ~(uint32_t) Y4_PF_ALIVE; W.ray[i] = y4_null_ray(); return; }   // reference: direction undefined
+	W.ray[i] = y4_mk_ray(sp.p, sc.ray_min_dist, wi, -1.f);
+	W.flags[i] = f | Y4_PF_ALIVE;
+}
+
+// ---- stage: the extended ray's hit (integrate(), :191-207 and :232-266) ----------------------------
+Y4_HD void y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub)
+{
+	uint32_t f = W.flags[i];
+	if(!(f & Y4_PF_ALIVE)) return;
+	const Y4Hit h = W.hit[i];
+	if(h.prim < 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return; }     // hit background: continue / break
+	const Y4Ray r = W.ray[i];
+	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
+	const Y4Surf sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
+	const Y4PtMaterial m = sc.mats[sp.mat];
+	const V3 pwo = xneg(d);
+	C3 emit = c3f(0.f);
+	bool direct;
+	if(depth == 0)
+	{
+		if(m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIFF1; else f &= ~(uint32_t) Y4_PF_DIFF1;
+		if(m.bsdf_flags & Y4_BSDF_EMIT) emit = y4_mat_emit(m, sp, pwo);
+		direct = m.is_diffuse != 0;     // a non-diffuse vertex evaluates to exactly 0 for every light sample
+	}
+	else
+	{
+		direct = (f & Y4_PF_DIFF1) && m.is_diffuse;
+		if(depth > sc.rr_min_bounces)
+		{
+			// the reference draws from a rand()-seeded per-tile generator (not reproducible); documented substitute
+			const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+			const float random_value = y4_hash_uniform(sc.rr_seed ^ s.offset, s.sample, (uint32_t) (sub * 64 + depth));
+			C3 thr = ld3(W.thr, i);
+			const float probability = cmax(thr);
+			if(probability <= 0.f || probability < random_value) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return; }
+			st3(W.thr, i, cscale(thr, xdiv(1.f, probability)));
+		}
+	}
+	if(sc.n_lights == 0) direct = false;
+	if(direct)
+	{
+		// light choice of estimateOneDirectLight: Halton(2) at base offset + a per-call counter.  The
+		// reference counter is per CPU thread (call-order dependent); here it is a per-vertex index.
+		const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+		const uint32_t corr = (W.pix[i] * 1009u + s.sample) * (uint32_t) (sc.bounces * sc.n_paths) + (uint32_t) (sub * sc.bounces + depth);
+		Y4Halton h2 = y4_halton_start(2u, sc.base_sampling_offset + corr - 1u);
+		const int lnum = (int) xmul(y4_halton_next(h2), (float) sc.n_lights);
+		W.lnum[i] = (uint32_t) (lnum < sc.n_lights - 1 ? lnum : sc.n_lights - 1);
+		st3(W.lcol, i, emit);
+		W.flags[i] = f | Y4_PF_DIRECT;
+	}
+	else
+	{
+		// lcol = 0 (* num_lights) + emit;  path_col += lcol * throughput
+		const C3 lcol = cadd(c3f(0.f), emit);
+		st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, ld3(W.thr, i))));
+		W.flags[i] = f & ~(uint32_t) Y4_PF_DIRECT;
+	}
+}
+
+// ---- stage: close the pixel-sample and splat it into the film ----------------------------------------
+#if defined(__CUDA_ARCH__)
+Y4_HD void y4_film_add(float *p, float v) { atomicAdd(p, v); }
+#else
+Y4_HD void y4_film_add(float *p, float v) { *p += v; }
+#endif
+Y4_HD int y4_round_to_int(double v) { return (int) (v + (0.5 - 1.4e-11)); }     // math::roundToInt (math.h:268-277)
+
+Y4_HD void y4_pt_finish_splat(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, float *film_w, float *film_rgba)
+{
+	const uint32_t f = W.flags[i];
+	C3 col = ld3(W.col, i);
+	float alpha = W.col[4ull * i + 3];
+	if(f & Y4_PF_PATHS) col = cadd(col, cdiv(ld3(W.pcol, i), (float) (sc.n_paths > 1 ? sc.n_paths : 1)));
+	if(alpha > 1.f) alpha = 1.f;
+	if(sc.clamp_samples > 0.f)      // Rgb::clampProportionalRgb (color.h:415-445)
+	{
+		const float max_rgb = fmaxf(col.r, fmaxf(col.g, col.b));
+		const float adj = xdiv(sc.clamp_samples, max_rgb);
+		if(max_rgb > sc.clamp_samples)
+		{
+			if(col.r >= max_rgb) { col.r = sc.clamp_samples; col.g = xmul(col.g, adj); col.b = xmul(col.b, adj); }
+			else if(col.g >= max_rgb) { col.g = sc.clamp_samples; col.r = xmul(col.r, adj); col.b = xmul(col.b, adj); }
+			else { col.b = sc.clamp_samples; col.r = xmul(col.r, adj); col.g = xmul(col.g, adj); }
+		}
+	}
+	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+	const int cx1 = sc.cx0 + sc.width, cy1 = sc.cy0 + sc.height;
+	int dx0 = y4_round_to_int((double) s.dx - sc.filterw), dx1 = y4_round_to_int((double) s.dx + sc.filterw - 1.0);
+	int dy0 = y4_round_to_int((double) s.dy - sc.filterw), dy1 = y4_round_to_int((double) s.dy + sc.filterw - 1.0);
+	if(dx0 < sc.cx0 - s.x) dx0 = sc.cx0 - s.x;
+	if(dx1 > cx1 - s.x - 1) dx1 = cx1 - s.x - 1;
+	if(dy0 < sc.cy0 - s.y) dy0 = sc.cy0 - s.y;
+	if(dy1 > cy1 - s.y - 1) dy1 = cy1 - s.y - 1;
+	const double x_offs = (double) s.dx - 0.5, y_offs = (double) s.dy - 0.5;
+	for(int jj = dy0; jj <= dy1; ++jj)
+	{
+		const int yi = (int) floor(fabs(((double) jj - y_offs) * sc.table_scale));
+		for(int ii = dx0; ii <= dx1; ++ii)
+		{
+			const int xi = (int) floor(fabs(((double) ii - x_offs) * sc.table_scale));
+			const float wt = sc.filter_table[yi * Y4_FILTER_TABLE + xi];
+			const size_t p = (size_t) (s.y + jj - sc.cy0) * (size_t) sc.width + (size_t) (s.x + ii - sc.cx0);
+			y4_film_add(film_w + p, wt);
+			y4_film_add(film_rgba + 4 * p + 0, xmul(col.r, wt));
+			y4_film_add(film_rgba + 4 * p + 1, xmul(col.g, wt));
+			y4_film_add(film_rgba + 4 * p + 2, xmul(col.b, wt));
+			y4_film_add(film_rgba + 4 * p + 3, xmul(alpha, wt));
+		}
+	}
+}

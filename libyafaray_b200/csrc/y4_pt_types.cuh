@@ -1,0 +1,102 @@
+// Device-side scene description and per-path state of the wavefront path tracer.
+// Everything is derived on the host (y4_pt_host.cpp) from the parameter-level C-ABI structs with
+// the reference's own fp32 operation order, then uploaded once per y4gpu_pt_set_scene.
+#pragma once
+#include "y4_common.cuh"
+#include "y4_pt_sampling.cuh"
+#include "../../include/y4gpu.h"
+
+struct C3 { float r, g, b; };
+Y4_HD C3 c3(float r, float g, float b) { C3 c; c.r = r; c.g = g; c.b = b; return c; }
+Y4_HD C3 c3f(float v) { return c3(v, v, v); }
+// Rgb operators of include/color/color.h:258-295 (component-wise, float * Rgb is {f*r, f*g, f*b})
+Y4_HD C3 cmul(C3 a, C3 b) { return c3(xmul(a.r, b.r), xmul(a.g, b.g), xmul(a.b, b.b)); }
+Y4_HD C3 cscale(C3 a, float f) { return c3(xmul(f, a.r), xmul(f, a.g), xmul(f, a.b)); }
+Y4_HD C3 cdiv(C3 a, float f) { return c3(xdiv(a.r, f), xdiv(a.g, f), xdiv(a.b, f)); }
+Y4_HD C3 cadd(C3 a, C3 b) { return c3(xadd(a.r, b.r), xadd(a.g, b.g), xadd(a.b, b.b)); }
+Y4_HD bool cblack(C3 a) { return a.r == 0.f && a.g == 0.f && a.b == 0.f; }
+Y4_HD float cmax(C3 a) { return fmaxf(a.r, fmaxf(a.g, a.b)); }
+
+// BsdfFlags bits (include/material/material.h:44-62)
+enum : uint32_t
+{
+	Y4_BSDF_SPECULAR = 1u << 0, Y4_BSDF_GLOSSY = 1u << 1, Y4_BSDF_DIFFUSE = 1u << 2, Y4_BSDF_DISPERSIVE = 1u << 3,
+	Y4_BSDF_REFLECT = 1u << 4, Y4_BSDF_TRANSMIT = 1u << 5, Y4_BSDF_FILTER = 1u << 6, Y4_BSDF_EMIT = 1u << 7,
+	Y4_BSDF_ALL = 0x7fu
+};
+
+struct Y4PtCamera          // PerspectiveCamera state after ctor + setAxis (camera.cc:51-71, camera_perspective.cc:50-69)
+{
+	V3 pos, vright, vup, vto;
+	V3 near_p, near_n, far_p, far_n;
+	int resx, resy;
+};
+
+struct Y4PtMaterial
+{
+	int type;                   // Y4GPU_MAT_*
+	uint32_t bsdf_flags;        // Material::bsdf_flags_
+	C3 color;                   // diffuse_color_ / light_col_ (colour * power)
+	C3 emit;                    // emit_color_ = emit_strength * diffuse_color
+	float diffuse_strength;     // components_[3] (0 when !is_diffuse_)
+	int is_diffuse;
+	int oren_nayar; float oren_a, oren_b;
+	int double_sided, receive_shadows, flat_material;
+};
+
+struct Y4PtLight
+{
+	int type;                   // Y4GPU_LIGHT_*
+	int samples, cast_shadows;
+	C3 color;                   // point: col*inte ; area: col*inte*pi
+	V3 pos;                     // point position / area corner
+	V3 to_x, to_y, fnormal, normal, c2, c3, c4;
+	float area, inv_area;
+};
+
+#define Y4_PT_MAX_LIGHTS 64
+#define Y4_FILTER_TABLE 16
+
+struct Y4PtScene
+{
+	Y4PtCamera cam;
+	// integrator
+	int bounces, n_paths, rr_min_bounces, no_recursive, transp_background;
+	C3 background;
+	float shadow_bias; int shadow_bias_auto;
+	float ray_min_dist; int ray_min_dist_auto;
+	uint32_t base_sampling_offset, rr_seed;
+	float aa_light_sample_multiplier;
+	int aa_passes;
+	// film
+	int width, height, cx0, cy0;
+	double filterw, table_scale;
+	float clamp_samples;
+	float filter_table[Y4_FILTER_TABLE * Y4_FILTER_TABLE];
+	// scene content
+	int n_lights, n_mats;
+	Y4PtLight lights[Y4_PT_MAX_LIGHTS];
+	const Y4PtMaterial *mats;       // device array
+	const float *verts;             // [n_tri * 9] world-space vertices in primitive order
+	const uint32_t *tri_flags;      // [n_tri] or null (material = flags >> 8)
+	const float *normals;           // [n_tri * 9] exported vertex normals or null
+	Y4LdsTables lds;                // Faure tables (device pointers)
+};
+
+// Surface point: the subset of SurfacePoint the supported materials/lights read
+// (include/geometry/surface.h:86-120, filled like primitive_triangle.cc:97-176).
+struct Y4Surf
+{
+	V3 p, ng, n, nu, nv;
+	uint32_t mat;
+};
+
+// per-path flag bits
+enum : uint32_t
+{
+	Y4_PF_ALIVE = 1u,            // path still being extended in the bounce loop
+	Y4_PF_HIT0 = 2u,             // camera ray hit a surface
+	Y4_PF_PATHS = 4u,            // primary material matches path_flags -> bounce loop runs
+	Y4_PF_DIFF1 = 8u,            // first path vertex's material has Diffuse (mat_bsd_fs, integrator_path_tracer.cc:196)
+	Y4_PF_DIRECT = 16u           // the current vertex wants a one-light estimate this depth
+};

@@ -61,7 +61,8 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 				hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
 				ray_i = mine; sp = 0; have = true;
 				// virtual parent of the root: child_base 0, imask = slot 0, hit bit at slot 0's priority
-				ngroup.x = 0u; ngroup.y = bvh.n_tris ? ((1u << (24u + rc.oct_inv)) | 1u) : 0u;
+				// empty scene or empty interval (the path tracer parks finished paths as null rays): nothing to visit
+				ngroup.x = 0u; ngroup.y = (bvh.n_tris && pr.t_hi > pr.t_lo) ? ((1u << (24u + rc.oct_inv)) | 1u) : 0u;
 			}
 		}
 		if(!__any_sync(0xffffffffu, have)) break;

@@ -1,0 +1,423 @@
+"""Host-side mirror of libYafaRay's C public API for the hot path (scene streaming + render), bound
+to the B200 back end through the C-ABI (include/y4gpu.h).
+
+Reference interface: include/public_api/yafaray_c_api.h:53-130 (`yafaray_*` functions; here the
+same names without the prefix, same argument order and meaning) -> Interface
+(src/interface/interface.cc) -> Scene (src/scene/scene.cc).  The "current ParamMap" semantics of
+`paramsSet*` / `paramsClearAll` / `create*` are kept (interface.cc:118-197).  What the reference
+would render with `scene_accelerator = <kd-tree>` + `type = pathtracing` on CPU threads is rendered
+here by the BVH8 accelerator + wavefront path tracer kernels.  Scene features outside the supported
+set (shinydiffusemat without mirror/transparency/nodes, light_mat, pointlight,
+arealight, perspective pinhole camera, constant background, pathtracing) raise Y4Error -- they are
+never approximated, and there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import numpy as np
+
+from . import _lib
+from ._lib import Y4Error
+from .accelerator import ACCELERATOR_TYPE, AcceleratorB200
+
+VIS = {"normal": (True, True), "no_shadows": (True, False), "shadow_only": (False, True), "invisible": (False, False)}  # (visible, casts shadows)
+GLOBAL_SHADOW_BIAS, GLOBAL_MIN_RAYDIST = 0.0005, 0.00005  # include/common/yafaray_common.h:28-29
+
+
+class _Mesh:
+    def __init__(self, name, params):
+        self.name = name
+        self.verts: List[tuple] = []
+        self.normals: List[tuple] = []
+        self.tris: List[tuple] = []
+        self.tri_mats: List[str] = []
+        self.visibility = params.get("visibility", "normal")
+        self.is_base = bool(params.get("is_base_object", False))
+        self.instance_of: Optional[str] = None
+        self.matrix = None
+
+
+class Interface:
+    """`yafaray_Interface_t` for the GPU back end: build a scene with the C API's calls, then render()."""
+
+    def __init__(self, device: int = 0, shard_index: int = 0, shard_count: int = 1):
+        self.device, self.shard_index, self.shard_count = device, shard_index, shard_count
+        self.params: Dict[str, object] = {}
+        self.materials: Dict[str, dict] = {}
+        self.lights: Dict[str, dict] = {}
+        self.cameras: Dict[str, dict] = {}
+        self.backgrounds: Dict[str, dict] = {}
+        self.integrators: Dict[str, dict] = {}
+        self.views: Dict[str, dict] = {}
+        self.objects: Dict[str, _Mesh] = {}
+        self.render_params: Dict[str, object] = {}
+        self._cur: Optional[_Mesh] = None
+        self._cur_mat: Optional[str] = None
+        self._next_id = 0
+        self.accelerator: Optional[AcceleratorB200] = None
+        self.film_buffers = None  # optional (weights, rgba) torch CUDA tensors installed by the caller
+        self.last_stats: dict = {}
+
+    # ---- the "current ParamMap" (interface.cc:118-181) -------------------------------------------
+    def paramsClearAll(self):
+        self.params = {}
+
+    def paramsSetString(self, name, s):
+        self.params[name] = str(s)
+
+    def paramsSetBool(self, name, b):
+        self.params[name] = bool(b)
+
+    def paramsSetInt(self, name, i):
+        self.params[name] = int(i)
+
+    def paramsSetFloat(self, name, f):
+        self.params[name] = float(f)
+
+    def paramsSetVector(self, name, x, y, z):
+        self.params[name] = (float(x), float(y), float(z))
+
+    def paramsSetColor(self, name, r, g, b, a=1.0):
+        self.params[name] = (float(r), float(g), float(b), float(a))
+
+    def paramsPushList(self):
+        raise Y4Error("shader-node parameter lists (paramsPushList) are not supported by the GPU back end")
+
+    def paramsEndList(self):
+        pass
+
+    # ---- object factories (scene.cc:363-526) ------------------------------------------------------
+    def createMaterial(self, name):
+        p = dict(self.params)
+        t = p.get("type")
+        if t == "shinydiffusemat":
+            for k in ("specular_reflect", "transparency", "translucency"):
+                if float(p.get(k, 0.0)) != 0.0:
+                    raise Y4Error(f"shinydiffusemat '{name}': {k} != 0 is not supported by the GPU back end")
+            if p.get("fresnel_effect", False):
+                raise Y4Error(f"shinydiffusemat '{name}': fresnel_effect is not supported by the GPU back end")
+            for k in p:
+                if k.endswith("_shader"):
+                    raise Y4Error(f"shinydiffusemat '{name}': shader nodes are not supported by the GPU back end")
+        elif t != "light_mat":
+            raise Y4Error(f"material type '{t}' is not supported by the GPU back end")
+        self.materials[name] = p
+        return True
+
+    def createLight(self, name):
+        p = dict(self.params)
+        if p.get("type") not in ("pointlight", "arealight"):
+            raise Y4Error(f"light type '{p.get('type')}' is not supported by the GPU back end")
+        self.lights[name] = p
+        return True
+
+    def createCamera(self, name):
+        p = dict(self.params)
+        if p.get("type") != "perspective":
+            raise Y4Error(f"camera type '{p.get('type')}' is not supported by the GPU back end")
+        self.cameras[name] = p
+        return True
+
+    def createBackground(self, name):
+        p = dict(self.params)
+        if p.get("type") != "constant" or p.get("ibl", False):
+            raise Y4Error("only a constant background without IBL is supported by the GPU back end")
+        self.backgrounds[name] = p
+        return True
+
+    def createIntegrator(self, name):
+        p = dict(self.params)
+        if p.get("type") != "pathtracing":
+            raise Y4Error(f"integrator type '{p.get('type')}' is not supported by the GPU back end")
+        if p.get("caustic_type", "path") in ("photon", "both"):
+            raise Y4Error("photon caustics are not supported by the GPU back end")
+        if p.get("transpShad", False) or p.get("do_AO", False):
+            raise Y4Error("transparent shadows / AO in the path tracer are not supported by the GPU back end yet")
+        self.integrators[name] = p
+        return True
+
+    def createRenderView(self, name):
+        self.views[name] = dict(self.params)
+        return True
+
+    def createOutput(self, name):
+        return True  # image files are written by the host application from the film (out of scope)
+
+    def defineLayer(self):
+        if self.params.get("type", "combined") != "combined":
+            raise Y4Error("only the Combined layer is produced by the GPU back end")
+
+    # ---- geometry streaming (scene.cc:900-1030) ---------------------------------------------------
+    def startGeometry(self):
+        return True
+
+    def endGeometry(self):
+        return True
+
+    def getNextFreeId(self):
+        self._next_id += 1
+        return self._next_id
+
+    def createObject(self, name):
+        p = dict(self.params)
+        if p.get("type") != "mesh":
+            raise Y4Error(f"object type '{p.get('type')}' is not supported by the GPU back end")
+        self._cur = _Mesh(name, p)
+        self.objects[name] = self._cur
+        return True
+
+    def setCurrentMaterial(self, name):
+        if name not in self.materials:
+            raise Y4Error(f"unknown material '{name}'")
+        self._cur_mat = name
+
+    def addVertex(self, x, y, z):
+        self._cur.verts.append((x, y, z))
+        return len(self._cur.verts) - 1
+
+    def addNormal(self, x, y, z):
+        self._cur.normals.append((x, y, z))
+
+    def addTriangle(self, a, b, c):
+        self._cur.tris.append((a, b, c))
+        self._cur.tri_mats.append(self._cur_mat)
+        return True
+
+    def add_mesh_arrays(self, verts: np.ndarray, tris: np.ndarray):
+        """Bulk form of addVertex/addTriangle for large procedural meshes (same semantics)."""
+        base = len(self._cur.verts)
+        self._cur.verts.extend(map(tuple, np.asarray(verts, np.float64).reshape(-1, 3)))
+        for t in np.asarray(tris, np.int64).reshape(-1, 3):
+            self._cur.tris.append((base + int(t[0]), base + int(t[1]), base + int(t[2])))
+            self._cur.tri_mats.append(self._cur_mat)
+
+    def endObject(self):
+        self._cur = None
+        return True
+
+    def smoothMesh(self, name, angle):
+        raise Y4Error("smoothMesh is not supported by the GPU back end (export vertex normals with addNormal instead)")
+
+    def addInstance(self, base_object_name, *m):
+        if base_object_name not in self.objects:
+            raise Y4Error(f"base mesh '{base_object_name}' for instance does not exist")
+        inst = _Mesh(f"{base_object_name}-{self.getNextFreeId()}", {})
+        inst.instance_of = base_object_name
+        inst.matrix = np.array(m, np.float32).reshape(4, 4)
+        self.objects[inst.name] = inst
+        return True
+
+    # ---- render set-up (scene.cc:528-644) ------------------------------------------------------------
+    def setupRender(self):
+        self.render_params = dict(self.params)
+        acc = self.render_params.get("scene_accelerator", ACCELERATOR_TYPE)
+        if acc != ACCELERATOR_TYPE:
+            raise Y4Error(f"scene_accelerator '{acc}' is not provided by this back end (use '{ACCELERATOR_TYPE}')")
+
+    # ---- scene assembly: what Scene::updateObjects + the factories hand to the back end --------------
+    def assemble(self):
+        """-> dict(tris [n,9] f32, flags [n] u32, normals [n,9] f32 | None, cam, mats, lights, params) in the
+        reference's orders: objects by name (std::map, scene.cc:1034), faces in insertion order, lights by name."""
+        mat_names = list(self.materials)
+        mat_index = {n: i for i, n in enumerate(mat_names)}
+        tris, flags, normals, any_normals = [], [], [], False
+        for name in sorted(self.objects):
+            o = self.objects[name]
+            base = self.objects[o.instance_of] if o.instance_of else o
+            vis_o, sh_o = VIS[o.visibility if not o.instance_of else base.visibility]
+            if (not vis_o and not sh_o) or o.is_base:
+                continue
+            if not base.tris:
+                continue
+            v = np.asarray(base.verts, np.float64).astype(np.float32)  # API doubles are narrowed to float (interface.cc:87)
+            if o.instance_of:  # Matrix4 * Point3 in fp32, matrix4.h:85-90
+                m = o.matrix
+                v = np.stack([((m[r, 0] * v[:, 0] + m[r, 1] * v[:, 1]) + m[r, 2] * v[:, 2]) + m[r, 3] for r in range(3)], -1).astype(np.float32)
+            idx = np.asarray(base.tris, np.int64)
+            tris.append(v[idx].reshape(-1, 9))
+            if base.normals and len(base.normals) == len(base.verts) and not o.instance_of:
+                nn = np.asarray(base.normals, np.float64).astype(np.float32)
+                normals.append(nn[idx].reshape(-1, 9))
+                any_normals = True
+            else:
+                normals.append(None)
+            f = np.empty(len(idx), np.uint32)
+            for k, mn in enumerate(base.tri_mats):
+                if mn is None:
+                    raise Y4Error(f"object '{name}': triangle without a material")
+                vis_m, sh_m = VIS[self.materials[mn].get("visibility", "normal")]
+                w = (mat_index[mn] << _lib.TRI_MAT_SHIFT)
+                if vis_o and vis_m:
+                    w |= _lib.TRI_VIS_CLOSEST
+                if sh_o and sh_m:
+                    w |= _lib.TRI_VIS_SHADOW
+                if sh_m:
+                    w |= _lib.TRI_VIS_TSHADOW
+                f[k] = w
+            flags.append(f)
+        if tris:
+            T = np.ascontiguousarray(np.concatenate(tris), np.float32)
+            F = np.ascontiguousarray(np.concatenate(flags), np.uint32)
+        else:
+            T, F = np.zeros((0, 9), np.float32), np.zeros(0, np.uint32)
+        N = None
+        if any_normals:
+            if any(x is None for x in normals):
+                raise Y4Error("exported vertex normals on only a subset of the objects are not supported yet")
+            N = np.ascontiguousarray(np.concatenate(normals), np.float32)
+
+        rp = self.render_params
+        integ = self.integrators[rp["integrator_name"]] if "integrator_name" in rp else next(iter(self.integrators.values()))
+        bg = self.backgrounds.get(rp.get("background_name", ""), None)
+        view = next(iter(self.views.values())) if self.views else {}
+        cam_p = self.cameras[view["camera_name"]] if "camera_name" in view else next(iter(self.cameras.values()))
+
+        cam = _lib.PtCamera()
+        cam.from_[:] = cam_p.get("from", (0.0, 1.0, 0.0))
+        cam.to[:] = cam_p.get("to", (0.0, 0.0, 0.0))
+        cam.up[:] = cam_p.get("up", (0.0, 1.0, 1.0))
+        cam.resx, cam.resy = int(cam_p.get("resx", 320)), int(cam_p.get("resy", 200))
+        cam.aspect_ratio, cam.focal = float(cam_p.get("aspect_ratio", 1.0)), float(cam_p.get("focal", 1.0))
+        cam.aperture, cam.dof_distance = float(cam_p.get("aperture", 0.0)), float(cam_p.get("dof_distance", 0.0))
+        cam.near_clip, cam.far_clip = float(cam_p.get("nearClip", 0.0)), float(cam_p.get("farClip", -1.0))
+
+        mats = (_lib.PtMaterial * max(1, len(mat_names)))()
+        for i, n in enumerate(mat_names):
+            p, m = self.materials[n], mats[i]
+            m.color[:] = p.get("color", (1.0, 1.0, 1.0, 1.0))[:3]
+            m.receive_shadows, m.flat_material = int(p.get("receive_shadows", True)), int(p.get("flat_material", False))
+            if p["type"] == "light_mat":
+                m.type, m.emit, m.double_sided = _lib.MAT_LIGHT, float(p.get("power", 1.0)), int(p.get("double_sided", False))
+            else:
+                m.type, m.diffuse_reflect, m.emit = _lib.MAT_SHINYDIFFUSE, float(p.get("diffuse_reflect", 1.0)), float(p.get("emit", 0.0))
+                if p.get("diffuse_brdf", "lambert") == "oren_nayar":
+                    m.oren_nayar, m.sigma = 1, float(p.get("sigma", 0.1))
+
+        wanted = [s for s in str(view.get("light_names", "")).split(";") if s]
+        light_names = [n for n in sorted(self.lights) if self.lights[n].get("light_enabled", True) and (not wanted or n in wanted)]
+        lights = (_lib.PtLight * max(1, len(light_names)))()
+        for i, n in enumerate(light_names):
+            p, l = self.lights[n], lights[i]
+            if p.get("photon_only", False):
+                raise Y4Error("photon_only lights are not supported by the GPU back end")
+            l.color[:] = p.get("color", (1.0, 1.0, 1.0, 1.0))[:3]
+            l.power, l.cast_shadows = float(p.get("power", 1.0)), int(p.get("cast_shadows", True))
+            if p["type"] == "pointlight":
+                l.type = _lib.LIGHT_POINT
+                l.from_[:] = p.get("from", (0.0, 0.0, 0.0))
+            else:
+                l.type, l.samples = _lib.LIGHT_AREA, int(p.get("samples", 4))
+                l.from_[:] = p.get("corner", (0.0, 0.0, 0.0))
+                l.point1[:] = p.get("point1", (0.0, 0.0, 0.0))
+                l.point2[:] = p.get("point2", (0.0, 0.0, 0.0))
+
+        pr = _lib.PtParams()
+        pr.bounces, pr.path_samples = int(integ.get("bounces", 3)), int(integ.get("path_samples", 32))
+        pr.russian_roulette_min_bounces, pr.no_recursive = int(integ.get("russian_roulette_min_bounces", 0)), int(integ.get("no_recursive", False))
+        pr.transp_background = int(integ.get("bg_transp", False))
+        if bg is not None:
+            c, pw = bg.get("color", (0.0, 0.0, 0.0, 1.0)), np.float32(bg.get("power", 1.0))
+            pr.background[:] = [float(np.float32(c[k]) * pw) for k in range(3)]
+        pr.width, pr.height = int(rp.get("width", cam.resx)), int(rp.get("height", cam.resy))
+        pr.xstart, pr.ystart = int(rp.get("xstart", 0)), int(rp.get("ystart", 0))
+        pr.aa_passes, pr.aa_samples, pr.aa_inc_samples = int(rp.get("AA_passes", 1)), int(rp.get("AA_minsamples", 1)), int(rp.get("AA_inc_samples", 1))
+        pr.aa_sample_multiplier_factor = float(rp.get("AA_sample_multiplier_factor", 1.0))
+        pr.aa_light_sample_multiplier_factor = float(rp.get("AA_light_sample_multiplier_factor", 1.0))
+        pr.aa_pixelwidth, pr.aa_clamp_samples = float(rp.get("AA_pixelwidth", 1.5)), float(rp.get("AA_clamp_samples", 0.0))
+        ft = str(rp.get("filter_type", "box"))
+        pr.filter_type = _lib.FILTERS.get(ft, 0)
+        pr.shadow_bias_auto = int(rp.get("adv_auto_shadow_bias_enabled", True))
+        pr.shadow_bias = GLOBAL_SHADOW_BIAS if pr.shadow_bias_auto else float(rp.get("adv_shadow_bias_value", GLOBAL_SHADOW_BIAS))
+        pr.min_raydist_auto = int(rp.get("adv_auto_min_raydist_enabled", True))
+        pr.min_raydist = GLOBAL_MIN_RAYDIST if pr.min_raydist_auto else float(rp.get("adv_min_raydist_value", GLOBAL_MIN_RAYDIST))
+        pr.base_sampling_offset = (int(rp.get("adv_base_sampling_offset", 0)) + 100000 * int(rp.get("adv_computer_node", 0))) & 0xFFFFFFFF
+        pr.rr_seed = int(rp.get("b200_rr_seed", 0x5EED)) & 0xFFFFFFFF
+        pr.wave_size = int(rp.get("b200_wave_size", 0))
+        return {"tris": T, "flags": F, "normals": N, "cam": cam, "mats": mats, "n_mat": len(mat_names), "lights": lights,
+                "n_light": len(light_names), "params": pr}
+
+    # ---- render (Scene::render -> TiledIntegrator::render, integrator_tiled.cc:97-233) --------------
+    def upload(self):
+        """Geometry upload + BVH8 build + scene description (the accelerator/integrator preprocess step)."""
+        a = self.assemble()
+        if self.accelerator is not None:
+            self.accelerator.close()
+        self.accelerator = AcceleratorB200(a["tris"], flags=a["flags"], device=self.device)
+        L, ctx = self.accelerator._L, self.accelerator.ctx
+        nptr = C.c_void_p(a["normals"].ctypes.data) if a["normals"] is not None else None
+        _lib.check(ctx, L.y4gpu_pt_set_scene(ctx, C.byref(a["cam"]), a["mats"], a["n_mat"], a["lights"], a["n_light"], C.byref(a["params"]), nptr), "y4gpu_pt_set_scene")
+        if self.film_buffers is not None:
+            w, rgba = self.film_buffers
+            _lib.check(ctx, L.y4gpu_pt_set_film_buffers(ctx, C.c_void_p(w.data_ptr()), C.c_void_p(rgba.data_ptr())), "y4gpu_pt_set_film_buffers")
+        self._assembled = a
+        return a
+
+    def render_pass(self, n_samples: int, offset: int, aa_pass: int, pixel_list=None):
+        """TiledIntegrator::renderPass(samples, offset, adaptive, aa_pass_number) on this GPU's shard."""
+        L, ctx = self.accelerator._L, self.accelerator.ctx
+        if pixel_list is None:
+            ptr, n = None, 0
+        elif hasattr(pixel_list, "data_ptr"):
+            ptr, n = C.c_void_p(pixel_list.data_ptr()), int(pixel_list.numel())
+        else:
+            pixel_list = np.ascontiguousarray(pixel_list, np.uint32)
+            ptr, n = C.c_void_p(pixel_list.ctypes.data), int(pixel_list.size)
+        _lib.check(ctx, L.y4gpu_pt_render_pass(ctx, int(n_samples), int(offset), int(aa_pass), ptr, n, self.shard_index, self.shard_count), "y4gpu_pt_render_pass")
+
+    def render(self, monitor_callback=None):
+        """yafaray_render: pass 0 with AA_minsamples, then AA_passes-1 passes of ceil(AA_inc_samples * mult)
+        samples over all pixels (adaptive resampling by ImageFilm::nextPass is a host-side 'next' row: with
+        AA_threshold > 0 and AA_passes > 1 the render is refused).  Returns the normalised Combined layer."""
+        a = self.upload()
+        pr, rp = a["params"], self.render_params
+        if pr.aa_passes > 1 and float(rp.get("AA_threshold", 0.05)) > 0.0:
+            raise Y4Error("adaptive multi-pass AA (AA_threshold > 0) is not supported by the GPU back end yet; set AA_threshold = 0")
+        L, ctx = self.accelerator._L, self.accelerator.ctx
+        _lib.check(ctx, L.y4gpu_pt_clear_film(ctx), "y4gpu_pt_clear_film")
+        stats = {"samples": 0, "rays_closest": 0, "rays_shadow": 0, "kernel_launches": 0, "pass_ms": 0.0}
+        self.render_pass(pr.aa_samples, 0, 0)
+        self._add_stats(stats)
+        acum, mult = pr.aa_samples, np.float32(1.0)
+        for i in range(1, pr.aa_passes):
+            mult = np.float32(mult * np.float32(pr.aa_sample_multiplier_factor))
+            n = int(np.ceil(np.float32(pr.aa_inc_samples) * mult))
+            self.render_pass(n, acum, i)
+            self._add_stats(stats)
+            acum += n
+        self.last_stats = stats
+        return self.read_image()
+
+    def _add_stats(self, acc):
+        self.accelerator.synchronize()
+        s = _lib.PtStats()
+        L, ctx = self.accelerator._L, self.accelerator.ctx
+        _lib.check(ctx, L.y4gpu_pt_get_stats(ctx, C.byref(s)), "y4gpu_pt_get_stats")
+        for k in acc:
+            acc[k] += getattr(s, k)
+
+    def read_film(self):
+        """-> (weights [h, w], rgba [h, w, 4]) as accumulated (ImageFilm::weights_ and the Combined layer)."""
+        pr = self._assembled["params"]
+        w = np.empty((pr.height, pr.width), np.float32)
+        rgba = np.empty((pr.height, pr.width, 4), np.float32)
+        L, ctx = self.accelerator._L, self.accelerator.ctx
+        _lib.check(ctx, L.y4gpu_pt_read_film(ctx, C.c_void_p(w.ctypes.data), C.c_void_p(rgba.ctypes.data)), "y4gpu_pt_read_film")
+        return w, rgba
+
+    def read_image(self):
+        """ImageFilm::flush normalisation (imagefilm.cc:598-600, Rgba::normalized): colour / weight, 0 where weight == 0."""
+        w, rgba = self.read_film()
+        return normalize_film(w, rgba)
+
+    def clearAll(self):
+        if self.accelerator is not None:
+            self.accelerator.close()
+            self.accelerator = None
+
+
+def normalize_film(w: np.ndarray, rgba: np.ndarray) -> np.ndarray:
+    """Rgba::normalized(weight): `*this / weight` with Rgba operator/ = multiply by 1.f / weight (color.h:312-316,554-558)."""
+    inv = np.where(w != 0, np.float32(1.0) / np.where(w != 0, w, np.float32(1.0)), np.float32(0.0)).astype(np.float32)
+    return (rgba * inv[..., None]).astype(np.float32)

@@ -1,7 +1,7 @@
 """Synthetic procedural scenes and ray batches.
 
 Everything is generated on the host with numpy from fixed seeds so that the
-reference oracle (oracle/_ref/ref_raybatch) and the CUDA path see byte-identical
+reference-based checker used by the tests and the CUDA path see byte-identical
 inputs.  Triangles are returned as float32 [n_tri, 9] (v0 v1 v2, world space);
 triangle i is primitive index i (reference: Scene::updateObjects ordering,
 /root/reference/src/scene/scene.cc:1032-1041).  Rays are float32 [n, 8] =

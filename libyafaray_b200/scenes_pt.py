@@ -1,0 +1,164 @@
+"""Procedural path-tracer scenes expressed as calls on a libYafaRay-style
+C-API object (reference: include/public_api/yafaray_c_api.h:53-130; parameter names per
+SURVEY.md appendix A).  `api` is anything with the C API's method names minus the `yafaray_`
+prefix: libyafaray_b200.interface.Interface (the product) or a script recorder that replays the
+same calls against the unmodified reference (oracle/harness/ref_render.cc) -- so both renderers
+are driven by the very same call sequence."""
+from __future__ import annotations
+
+import numpy as np
+
+
+def _material(api, name, color, diffuse_reflect=1.0, **extra):
+    api.paramsClearAll()
+    api.paramsSetString("type", "shinydiffusemat")
+    api.paramsSetColor("color", color[0], color[1], color[2], 1.0)
+    api.paramsSetFloat("diffuse_reflect", diffuse_reflect)
+    for k, v in extra.items():
+        if isinstance(v, str):
+            api.paramsSetString(k, v)
+        elif isinstance(v, bool):
+            api.paramsSetBool(k, v)
+        else:
+            api.paramsSetFloat(k, float(v))
+    api.createMaterial(name)
+
+
+def _mesh(api, name, material, verts, tris):
+    api.paramsClearAll()
+    api.paramsSetString("type", "mesh")
+    api.paramsSetInt("num_vertices", len(verts))
+    api.paramsSetInt("num_faces", len(tris))
+    api.createObject(name)
+    api.setCurrentMaterial(material)
+    for v in verts:
+        api.addVertex(float(v[0]), float(v[1]), float(v[2]))
+    for t in tris:
+        api.addTriangle(int(t[0]), int(t[1]), int(t[2]))
+    api.endObject()
+
+
+def _quad(p0, p1, p2, p3):
+    return [p0, p1, p2, p3], [(0, 1, 2), (0, 2, 3)]
+
+
+def _box(lo, hi, yaw_deg, centre):
+    """Axis-aligned box [lo, hi] rotated by yaw about the vertical through `centre`; no bottom face."""
+    x0, y0, z0 = lo
+    x1, y1, z1 = hi
+    c = np.array([[x0, y0, z0], [x1, y0, z0], [x1, y0, z1], [x0, y0, z1], [x0, y1, z0], [x1, y1, z0], [x1, y1, z1], [x0, y1, z1]], np.float64)
+    a = np.radians(yaw_deg)
+    r = np.array([[np.cos(a), 0, np.sin(a)], [0, 1, 0], [-np.sin(a), 0, np.cos(a)]])
+    ctr = np.array(centre, np.float64)
+    c = (c - ctr) @ r.T + ctr
+    faces = [(4, 7, 6, 5), (0, 1, 5, 4), (1, 2, 6, 5), (2, 3, 7, 6), (3, 0, 4, 7), (0, 3, 2, 1)]
+    tris = []
+    for f in faces:
+        tris += [(f[0], f[1], f[2]), (f[0], f[2], f[3])]
+    return c.astype(np.float32), tris
+
+
+def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
+                aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
+                oren_nayar=False, integrator="pathtracing"):
+    """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes."""
+    white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
+    extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
+    _material(api, "white", white, **extra)
+    _material(api, "red", red, **extra)
+    _material(api, "green", green, **extra)
+    api.paramsClearAll()
+    api.paramsSetString("type", "light_mat")
+    api.paramsSetColor("color", 1.0, 0.85, 0.6, 1.0)
+    api.paramsSetFloat("power", 18.0)
+    api.createMaterial("emitter")
+
+    api.startGeometry()
+    v, t = _quad((0, 0, 0), (1, 0, 0), (1, 0, 1), (0, 0, 1))
+    _mesh(api, "a_floor", "white", v, t)
+    v, t = _quad((0, 1, 0), (0, 1, 1), (1, 1, 1), (1, 1, 0))
+    _mesh(api, "b_ceiling", "white", v, t)
+    v, t = _quad((0, 0, 1), (1, 0, 1), (1, 1, 1), (0, 1, 1))
+    _mesh(api, "c_back", "white", v, t)
+    v, t = _quad((0, 0, 0), (0, 0, 1), (0, 1, 1), (0, 1, 0))
+    _mesh(api, "d_left", "red", v, t)
+    v, t = _quad((1, 0, 0), (1, 1, 0), (1, 1, 1), (1, 0, 1))
+    _mesh(api, "e_right", "green", v, t)
+    v, t = _box((0.53, 0.0, 0.53), (0.83, 0.6, 0.83), 18.0, (0.68, 0.0, 0.68))
+    _mesh(api, "f_tall", "white", v, t)
+    v, t = _box((0.18, 0.0, 0.2), (0.48, 0.3, 0.5), -17.0, (0.33, 0.0, 0.35))
+    _mesh(api, "g_short", "white", v, t)
+    # emitting quad just below the ceiling, facing down; the area light shares its corners
+    lx0, lx1, lz0, lz1, ly = 0.37, 0.63, 0.395, 0.605, 0.999
+    if not point_light:
+        v, t = _quad((lx0, ly, lz0), (lx1, ly, lz0), (lx1, ly, lz1), (lx0, ly, lz1))
+        _mesh(api, "h_lamp", "emitter", v, t)
+    api.endGeometry()
+
+    api.paramsClearAll()
+    if point_light:
+        api.paramsSetString("type", "pointlight")
+        api.paramsSetVector("from", 0.5, 0.9, 0.5)
+        api.paramsSetColor("color", 1.0, 0.85, 0.6, 1.0)
+        api.paramsSetFloat("power", 0.6)
+    else:
+        api.paramsSetString("type", "arealight")
+        api.paramsSetVector("corner", lx0, ly, lz0)
+        api.paramsSetVector("point1", lx1, ly, lz0)   # to_x = point1 - corner; emits toward to_x ^ to_y = -y
+        api.paramsSetVector("point2", lx0, ly, lz1)
+        api.paramsSetColor("color", 1.0, 0.85, 0.6, 1.0)
+        api.paramsSetFloat("power", 18.0)
+        api.paramsSetInt("samples", light_samples)
+        api.paramsSetString("object_name", "h_lamp")
+    api.createLight("lamp")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "perspective")
+    api.paramsSetVector("from", 0.5, 0.5, -1.35)
+    api.paramsSetVector("to", 0.5, 0.5, 0.0)
+    api.paramsSetVector("up", 0.5, 1.5, -1.35)
+    api.paramsSetInt("resx", width)
+    api.paramsSetInt("resy", height)
+    api.paramsSetFloat("focal", 1.6 * height / width if width > height else 1.6)
+    api.createCamera("cam")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "constant")
+    api.paramsSetColor("color", 0.0, 0.0, 0.0, 1.0)
+    api.createBackground("bg")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", integrator)
+    api.paramsSetInt("bounces", bounces)
+    api.paramsSetInt("path_samples", path_samples)
+    api.paramsSetInt("russian_roulette_min_bounces", bounces if rr_min_bounces is None else rr_min_bounces)
+    api.paramsSetString("caustic_type", "none")
+    api.paramsSetInt("raydepth", 2)
+    api.createIntegrator("pt")
+
+    api.paramsClearAll()
+    api.paramsSetString("camera_name", "cam")
+    api.createRenderView("view")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "combined")
+    api.paramsSetString("image_type", "ColorAlpha")
+    api.paramsSetString("exported_image_type", "ColorAlpha")
+    api.paramsSetString("exported_image_name", "Combined")
+    api.defineLayer()
+
+    api.paramsClearAll()
+    api.paramsSetString("integrator_name", "pt")
+    api.paramsSetString("background_name", "bg")
+    api.paramsSetString("scene_accelerator", accelerator)
+    api.paramsSetInt("width", width)
+    api.paramsSetInt("height", height)
+    api.paramsSetInt("threads", threads)
+    api.paramsSetInt("AA_passes", 1)
+    api.paramsSetInt("AA_minsamples", spp)
+    api.paramsSetInt("AA_inc_samples", 1)
+    api.paramsSetFloat("AA_pixelwidth", aa_pixelwidth)
+    api.paramsSetString("filter_type", filter_type)
+    api.paramsSetString("tiles_order", "linear")
+    api.paramsSetInt("tile_size", 32)
+    api.setupRender()

@@ -62,3 +62,41 @@ class RefServer:
 
     def __exit__(self, *a):
         self.close()
+
+
+class ScriptRecorder:
+    """Records C-API style calls (method name == C function minus `yafaray_`) as ref_render script lines."""
+
+    def __init__(self):
+        self.lines = []
+
+    def __getattr__(self, name):
+        if name.startswith("_"):
+            raise AttributeError(name)
+
+        def call(*args):
+            toks = [name]
+            for a in args:
+                if isinstance(a, bool):
+                    toks.append("1" if a else "0")
+                elif isinstance(a, float):
+                    toks.append(repr(float(a)))
+                else:
+                    toks.append(str(a))
+            self.lines.append(" ".join(toks))
+
+        return call
+
+
+def ref_render(recorder, env=None):
+    """Render a recorded scene with the UNMODIFIED reference -> (float32 [H, W, 4] linear RGBA, info)."""
+    with tempfile.TemporaryDirectory() as d:
+        sp, op = os.path.join(d, "scene.script"), os.path.join(d, "out.f32")
+        with open(sp, "w") as f:
+            f.write("\n".join(recorder.lines) + f"\nrender {op}\n")
+        e = dict(os.environ)
+        e.update(env or {})
+        out = subprocess.run([os.path.join(REF_DIR, "ref_render"), sp], capture_output=True, text=True, check=True, env=e)
+        info = json.loads(out.stdout.strip().splitlines()[-1])
+        img = np.fromfile(op, np.float32).reshape(info["height"], info["width"], 4)
+        return img, info

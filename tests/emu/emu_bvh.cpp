@@ -16,7 +16,7 @@ struct EmuBvh
 	int n = 0;
 };
 
-static void build(const float *verts, const uint32_t *flags, int n, int leaf_max, EmuBvh &out)
+void emu_build(const float *verts, const uint32_t *flags, int n, int leaf_max, EmuBvh &out)
 {
 	out.n = n;
 	if(n == 0) return;
@@ -74,7 +74,7 @@ int emu_build_trace(const float *verts, const uint32_t *flags, int n, const floa
                     Y4Hit *hits, uint64_t *stats_out)
 {
 	EmuBvh b;
-	build(verts, flags, n, leaf_max, b);
+	emu_build(verts, flags, n, leaf_max, b);
 	Y4Bvh8 bvh; bvh.nodes = b.nodes.data(); bvh.tris = b.tris.data(); bvh.n_tris = (uint32_t) n; bvh.consts = nullptr;
 	uint64_t sn = 0, st = 0;
 	for(int i = 0; i < m; ++i)

@@ -7,6 +7,8 @@ from /root/reference by `make -C oracle ref`).  Run in the build container only:
   rays_sphere.npz    <- oracle/_ref/ref_raybatch on scenes.displaced_sphere(40, 20): primary,
                         shadow and diffuse batches with the reference kd-tree's hit records
   rays_soup.npz      <- same on scenes.triangle_soup(3000) with incoherent + segment rays
+  pt_cornell.npz     <- oracle/_ref/ref_render (reference PathIntegrator + kd-tree through the C API,
+                        threads=1, tiles linear) on scenes_pt.cornell_box for the PT_GOLDEN configurations
 """
 import os
 import subprocess
@@ -20,6 +22,14 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import helpers  # noqa: E402
 from libyafaray_b200 import scenes  # noqa: E402
+
+
+# configurations of the committed path-tracer golden images (tests import this dict)
+PT_GOLDEN = {
+    "area_box": dict(width=96, height=54, spp=4, bounces=4),
+    "point_gauss": dict(width=96, height=54, spp=4, bounces=4, point_light=True, filter_type="gauss"),
+    "area3_oren_paths2": dict(width=64, height=36, spp=3, bounces=3, light_samples=3, oren_nayar=True, path_samples=2),
+}
 
 
 def main():
@@ -47,6 +57,15 @@ def main():
         bound = np.array(srv.info["bound"], np.float32)
     np.savez_compressed(os.path.join(HERE, "rays_soup.npz"), scene=np.array([3000]), incoherent=inc, segment=seg,
                         hit_incoherent=h_inc, hit_segment=h_seg, bound=bound)
+    # path tracer: reference PathIntegrator renders (deterministic mode) of the Cornell scene
+    from libyafaray_b200 import scenes_pt
+
+    out = {}
+    for key, kw in PT_GOLDEN.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+    np.savez_compressed(os.path.join(HERE, "pt_cornell.npz"), **out)
     print("golden fixtures written")
 
 

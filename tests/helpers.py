@@ -86,3 +86,30 @@ def compare_closest(got, ref, rel=1e-5):
 
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 from refserver import RefServer  # noqa: E402,F401
+
+from refserver import ScriptRecorder, ref_render  # noqa: E402,F401
+
+
+def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0):
+    """CPU emulation of the wavefront path tracer stages on an Interface.assemble() result -> (weights, rgba)."""
+    import ctypes as C
+
+    pr = a["params"]
+    n_samples = pr.aa_samples if n_samples is None else n_samples
+    w = np.zeros((pr.height, pr.width), np.float32)
+    rgba = np.zeros((pr.height, pr.width, 4), np.float32)
+    f = emu().emu_pt_render
+    f.restype = C.c_int
+    nptr = a["normals"].ctypes.data_as(C.c_void_p) if a["normals"] is not None else None
+    rc = f(C.byref(a["cam"]), a["mats"], C.c_uint32(a["n_mat"]), a["lights"], C.c_uint32(a["n_light"]), C.byref(pr), _p(a["tris"]), _p(a["flags"]),
+           C.c_int(len(a["tris"])), nptr, C.c_int(n_samples), C.c_int(offset), C.c_int(aa_pass), _p(w), _p(rgba))
+    assert rc == 0
+    return w, rgba
+
+
+def psnr(img, ref, peak=None):
+    """PSNR in dB over RGB, peak = max of the reference unless given."""
+    a, b = np.asarray(img, np.float64)[..., :3], np.asarray(ref, np.float64)[..., :3]
+    mse = np.mean((a - b) ** 2)
+    peak = float(b.max()) if peak is None else peak
+    return float("inf") if mse == 0 else 10.0 * np.log10(peak * peak / mse)
