@@ -28,8 +28,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "Mrays/s (closest-hit primary + any-hit shadow + cosine-diffuse closest-hit, 1M-triangle displaced sphere)"
-UNIT = "Mrays/s"
+METRIC = "path-traced Msamples/s (Cornell box 1920x1080, 8 bounces + NEE, reference sample sequences); ray-batch Mrays/s in `raybatch`"
+UNIT = "Msamples/s"
+RB_METRIC = "Mrays/s (closest-hit primary + any-hit shadow + cosine-diffuse closest-hit, 1M-triangle displaced sphere)"
+RB_UNIT = "Mrays/s"
 BATCHES = ("primary", "shadow", "diffuse")
 LIGHT = (2.0, 3.0, 4.0)
 SHADOW_BIAS, MIN_RAYDIST = 5.0e-4, 5.0e-5
@@ -44,9 +46,31 @@ def parse_args():
     ap.add_argument("--res", type=int, default=4096, help="primary grid is res x res rays (16 Mi at 4096)")
     ap.add_argument("--nu", type=int, default=1000, help="sphere longitude segments (nu * nu/2 * 2 triangles)")
     ap.add_argument("--cpu-sample-res", type=int, default=512, help="CPU legs trace a (res/k)^2 strided subsample")
+    ap.add_argument("--pt-width", type=int, default=1920)
+    ap.add_argument("--pt-height", type=int, default=1080)
+    ap.add_argument("--pt-spp", type=int, default=16, help="samples per pixel per GPU per step (one AA pass); the config's 1024 spp = 64 such steps")
+    ap.add_argument("--pt-bounces", type=int, default=8)
+    ap.add_argument("--cpu-pt-width", type=int, default=480)
+    ap.add_argument("--cpu-pt-height", type=int, default=270)
+    ap.add_argument("--cpu-pt-spp", type=int, default=4)
+    ap.add_argument("--no-raybatch", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
+
+
+def pt_config_dict(args):
+    return {
+        "workload": "C2 (BASELINE configs[1]): procedural Cornell box built through the C-API mirror, path tracer 1024 spp at "
+                    "%dx%d, %d bounces, 1 area light with MIS NEE, box filter; one step = one AA pass of %d spp per GPU "
+                    "(1024 spp = %d steps)" % (args.pt_width, args.pt_height, args.pt_bounces, args.pt_spp, max(1, 1024 // args.pt_spp)),
+        "width": args.pt_width, "height": args.pt_height, "spp_per_step_per_gpu": args.pt_spp, "bounces": args.pt_bounces,
+        "path_samples": 1, "russian_roulette": "off (min_bounces = bounces: the reference's deterministic mode)",
+        "samples_per_step_per_gpu": args.pt_width * args.pt_height * args.pt_spp,
+        "l2": "no flush needed: each wavefront streams > 500 MB of path state / rays / hits per bounce (> 126 MB L2)",
+        "sharding": "AA-pass samples s mod N per GPU, scene + BVH replicated, one NCCL all-reduce of the pass film (5 floats/pixel) per step",
+        "secondary": "`raybatch`: C3 (configs[2]) 1M-triangle sphere, 3 x 16 Mi ray batches per GPU per step",
+    }
 
 
 def config_dict(args):
@@ -206,20 +230,16 @@ def cpu_sample_batches_numpy(tris, res: int, server):
     return {"primary": prim, "shadow": scenes.shadow_rays(p, ok, LIGHT), "diffuse": scenes.diffuse_rays(p, n, ok)}
 
 
-def run_reference_arm(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
+def reference_raybatch(args):
+    """C3 ray batches through the UNMODIFIED reference kd-tree on the host cores -> dict."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import refserver
     from libyafaray_b200 import scenes
 
-    line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(args)}
+    line = {"impl": "reference", "metric": RB_METRIC, "unit": RB_UNIT, "steps": args.steps, "warmup": args.warmup, "config": config_dict(args)}
     if not refserver.have_ref():
         line["unavailable"] = "oracle/_ref/ref_raybatch is not built (run __graft_entry__.build() where /root/reference exists)"
-        print(json.dumps(line))
-        return
+        return line
     tris = scenes.displaced_sphere(args.nu, args.nu // 2)
     with refserver.RefServer(tris, threads=0) as srv:
         batches = cpu_sample_batches_numpy(tris, args.cpu_sample_res, srv)
@@ -239,13 +259,11 @@ def run_reference_arm(args):
             "value": value, "ms_per_step": total / args.steps * 1e3,
             "breakdown_mrays_s": {b: n * args.steps / per[b] * 1e-6 for b in BATCHES},
             "kd_build_s": srv.info["build_s"],
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "reference",
+            "cpu_baseline": {"value": value, "unit": RB_UNIT, "cores": threads, "kind": "reference",
                              "sample": "%dx%d primary grid + shadow + diffuse batches (%d rays each) per step; yafaray-kdtree-original, build (%.1f s, serial) not timed"
                                        % (args.cpu_sample_res, args.cpu_sample_res, n, srv.info["build_s"])},
-            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0,
         })
-    print(json.dumps(line))
+    return line
 
 
 # ------------------------------------------------------------------------------------------------
@@ -258,29 +276,13 @@ def load_peaks():
         return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md; MEASURED_PEAKS.json absent)"
 
 
-def run_b200_arm(args):
-    import torch
-    import torch.distributed as dist
-
+def raybatch_arm(args, env):
+    """C3 ray batches (device-resident + end-to-end with host buffers) -> dict on rank 0, None elsewhere."""
+    torch, dist = env["torch"], env["dist"]
+    world, rank, local, dev, barrier, sampler = env["world"], env["rank"], env["local"], env["dev"], env["barrier"], env["sampler"]
     from libyafaray_b200 import scenes
     from libyafaray_b200.accelerator import AcceleratorB200
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- this back end has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    sampler = ClockSampler(local) if rank == 0 else None
     tris = scenes.displaced_sphere(args.nu, args.nu // 2)
     acc = AcceleratorB200(tris, device=local)
     stream = torch.cuda.Stream(device=dev)
@@ -376,9 +378,8 @@ def run_b200_arm(args):
         achieved = alg[dom]["bytes_per_ray"] * n / (per_ms[dom] * 1e-3) * 1e-9
         value = 3.0 * n * world * args.steps / (total_ms * 1e-3) * 1e-6
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": config_dict(args),
+            "metric": RB_METRIC, "value": value, "unit": RB_UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "scaling": "weak", "config": config_dict(args),
             "breakdown_mrays_s": {b: n / per_ms[b] * 1e-3 for b in BATCHES},
             "hit_fraction": hit_frac,
             "bvh": {k: acc.stats()[k] for k in ("n_tris", "n_nodes", "node_bytes", "tri_bytes", "build_ms")},
@@ -393,19 +394,16 @@ def run_b200_arm(args):
             },
         }
         if e2e:
-            line["e2e"] = {"value": 3.0 * n * world * e2e["steps"] / (e2e_ms * 1e-3) * 1e-6, "unit": UNIT,
+            line["e2e"] = {"value": 3.0 * n * world * e2e["steps"] / (e2e_ms * 1e-3) * 1e-6, "unit": RB_UNIT,
                            "h2d_bytes_per_step": 3 * n * 32, "d2h_bytes_per_step": 3 * n * 16, "steps": e2e["steps"],
                            "identical_to_resident_run": e2e["identical_to_resident_run"],
                            "api": "AcceleratorB200.intersect/isShadowed -> y4gpu_trace with pinned host ray/hit buffers"}
-        if sampler:
-            line["clocks"] = sampler.finish()
         if world == 1 and not args.no_cpu_baseline:
             line.update(cpu_baseline_leg(args, torch, acc, tris, tris_d, rays, hits, kinds))
-        print(json.dumps(line))
-        sys.stdout.flush()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        acc.close()
+        return line
+    acc.close()
+    return None
 
 
 def cpu_baseline_leg(args, torch, acc, tris, tris_d, rays, hits, kinds):
@@ -415,7 +413,7 @@ def cpu_baseline_leg(args, torch, acc, tris, tris_d, rays, hits, kinds):
     import refserver
 
     if not refserver.have_ref():
-        return {"cpu_baseline": {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}}
+        return {"cpu_baseline": {"value": None, "unit": RB_UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}}
     stride = max(1, args.res // max(1, args.cpu_sample_res))
     g = torch.arange(stride // 2, args.res, stride, device=tris_d.device)
     idx = (g[:, None] * args.res + g[None, :]).reshape(-1)
@@ -441,7 +439,7 @@ def cpu_baseline_leg(args, torch, acc, tris, tris_d, rays, hits, kinds):
         threads, build_s = srv.info["threads"], srv.info["build_s"]
     total = sum(per.values())
     return {
-        "cpu_baseline": {"value": 3 * m / total * 1e-6, "unit": UNIT, "cores": threads, "kind": "reference",
+        "cpu_baseline": {"value": 3 * m / total * 1e-6, "unit": RB_UNIT, "cores": threads, "kind": "reference",
                          "breakdown_mrays_s": {b: m / per[b] * 1e-6 for b in BATCHES}, "kd_build_s": build_s,
                          "sample": "every %dth ray in x and y of each 16 Mi batch (%d rays per batch, mean of 2 repeats); "
                                    "yafaray-kdtree-original from oracle/_ref on all host threads, serial kd build not timed" % (stride, m)},
@@ -449,12 +447,223 @@ def cpu_baseline_leg(args, torch, acc, tris, tris_d, rays, hits, kinds):
     }
 
 
+# ------------------------------------------------------------------------------------------------
+# path tracer (BASELINE configs[1])
+def reference_pt(args):
+    """Reference PathIntegrator + kd-tree through the reference's own C API on all host threads, bounded sample."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refserver
+    from libyafaray_b200 import scenes_pt
+
+    if not refserver.have_ref("ref_render"):
+        return {"unavailable": "oracle/_ref/ref_render is not built"}
+    rec = refserver.ScriptRecorder()
+    scenes_pt.cornell_box(rec, width=args.cpu_pt_width, height=args.cpu_pt_height, spp=args.cpu_pt_spp, bounces=args.pt_bounces, threads=-1)
+    n = args.cpu_pt_width * args.cpu_pt_height * args.cpu_pt_spp
+    for _ in range(max(0, min(args.warmup, 1))):
+        refserver.ref_render(rec)
+    t = [refserver.ref_render(rec)[1]["render_s"] for _ in range(max(1, args.steps))]
+    return {"value": n * len(t) / sum(t) * 1e-6, "ms_per_step": sum(t) / len(t) * 1e3, "cores": os.cpu_count(),
+            "sample": "%dx%d at %d spp per step (%d pixel-samples), same scene / bounces / light as the GPU step; reference PathIntegrator + "
+                      "yafaray-kdtree-original through its C API, threads = all (%d)" % (args.cpu_pt_width, args.cpu_pt_height, args.cpu_pt_spp, n, os.cpu_count())}
+
+
+def run_reference_arm(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": pt_config_dict(args)}
+    r = reference_pt(args)
+    if "unavailable" in r:
+        line["unavailable"] = r["unavailable"]
+        print(json.dumps(line))
+        return
+    line.update({"value": r["value"], "ms_per_step": r["ms_per_step"],
+                 "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "reference", "sample": r["sample"]},
+                 "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0})
+    if not args.no_raybatch:
+        line["raybatch"] = reference_raybatch(args)
+    print(json.dumps(line))
+
+
+# algorithmic bytes per pixel-sample moved by the shading stages (DESIGN.md section 5): SoA state read + written
+SHADE_BYTES = {"gen": 8 + 32 + 4, "primary": 32 + 16 + 16 + 5 * 16 + 4, "bounce_sample": 100 + 52, "bounce_hit": 76 + 40,
+               "direct": 64 + 96, "resolve": 168 + 68, "splat": 44 + 5 * 4 * 2}
+
+
+def pt_arm(args, env):
+    torch, dist = env["torch"], env["dist"]
+    world, rank, local, dev, barrier, sampler = env["world"], env["rank"], env["local"], env["dev"], env["barrier"], env["sampler"]
+    from libyafaray_b200 import interface, scenes_pt
+    from libyafaray_b200.accelerator import ACCELERATOR_TYPE
+
+    W, H, spp, bounces = args.pt_width, args.pt_height, args.pt_spp, args.pt_bounces
+    stream = torch.cuda.Stream(device=dev)
+
+    def make(profile=0):
+        yi = interface.Interface(device=local, shard_index=rank, shard_count=world)
+        scenes_pt.cornell_box(yi, width=W, height=H, spp=spp * world, bounces=bounces, accelerator=ACCELERATOR_TYPE)
+        yi.render_params["b200_profile"] = profile
+        return yi
+
+    # film: [weights | rgba] in ONE tensor so that a pass is combined across GPUs by a single all-reduce
+    pass_film = torch.zeros(H * W * 5, device=dev, dtype=torch.float32)
+    total_film = torch.zeros_like(pass_film) if world > 1 else None
+    yi = make()
+    yi.film_buffers = (pass_film[: H * W], pass_film[H * W:])
+    yi.upload()
+    yi.accelerator.set_stream(stream.cuda_stream)
+
+    def step(k):
+        yi.render_pass(spp * world, k * spp * world, 0)      # this GPU renders the samples s with s mod N == rank
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.all_reduce(pass_film)                   # one NCCL sum over NVLink per pass (film merge is linear)
+                total_film.add_(pass_film)
+                pass_film.zero_()
+
+    for k in range(args.warmup):
+        step(k)
+    stream.synchronize()
+    barrier()
+    launches0 = yi.accelerator.stats()["kernel_launches"]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    w0 = time.time()
+    e0.record(stream)
+    for k in range(args.steps):
+        step(args.warmup + k)
+    e1.record(stream)
+    stream.synchronize()
+    barrier()
+    w1 = time.time()
+    if sampler:
+        sampler.mark(w0, w1)
+    total_ms = e0.elapsed_time(e1)
+    launches = yi.accelerator.stats()["kernel_launches"] - launches0 + (3 * args.steps if world > 1 else 0)
+    st = yi.pass_stats()
+    film = (total_film if world > 1 else pass_film)
+    wsum = float(film[: H * W].sum())
+    mean_rgb = float((film[H * W:].view(H * W, 4)[:, :3].sum(0) / max(wsum, 1e-30)).mean())
+
+    # ---- end to end: the whole render call with host-side scene + host film (upload, build, pass, D2H film) ----
+    e2e = None
+    if not args.no_e2e:
+        e_steps = max(1, min(args.steps, 5))
+        ye = make()
+        ye.upload()
+        ye.render_pass(spp * world, 0, 0)
+        ye.read_film()
+        barrier()
+        h2d = int(ye._assembled["tris"].nbytes + ye._assembled["flags"].nbytes + 4096)
+        t0 = time.perf_counter()
+        for k in range(e_steps):
+            ye.upload()                                      # host triangles/materials/lights/camera -> device, BVH8 build
+            ye.render_pass(spp * world, k * spp * world, 0)
+            fw, frgba = ye.read_film()                       # device -> host film (weights + rgba)
+        barrier()
+        e2e = {"ms": (time.perf_counter() - t0) * 1e3, "steps": e_steps, "h2d": h2d, "d2h": int(fw.nbytes + frgba.nbytes)}
+        ye.clearAll()
+
+    # ---- one profiled pass: device time per kernel class + BVH visit counters (for the roofline) ----
+    yp = make(profile=1)
+    yp.upload()
+    yp.render_pass(spp * world, 0, 0)
+    prof = yp.pass_stats()
+    yp.clearAll()
+
+    t = torch.tensor([total_ms, e2e["ms"] if e2e else 0.0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        yi.clearAll()
+        return None
+    n = W * H * spp                                           # pixel-samples per GPU per step
+    value = n * world * args.steps / (total_ms * 1e-3) * 1e-6
+    peak, peak_src = load_peaks()
+    names = ["fill+camera", "trace_closest", "trace_shadow", "hit+bounce shading", "light sampling+resolve", "splat"]
+    cms = prof["class_ms"][:6]
+    dom = int(np.argmax(cms))
+    live = {1: prof["live_closest"], 2: prof["live_shadow"]}
+    n_lights_rounds = 1 + bounces                             # one light, one sample: direct+resolve rounds per pixel-sample
+    alg_bytes = {
+        0: n * SHADE_BYTES["gen"],
+        1: prof["rays_closest"] * 48 + prof["nodes_closest"] * 80 + prof["tris_closest"] * 48,
+        2: prof["rays_shadow"] * 48 + prof["nodes_shadow"] * 80 + prof["tris_shadow"] * 48,
+        3: n * (SHADE_BYTES["primary"] + bounces * (SHADE_BYTES["bounce_sample"] + SHADE_BYTES["bounce_hit"])),
+        4: n * n_lights_rounds * (SHADE_BYTES["direct"] + SHADE_BYTES["resolve"]),
+        5: n * SHADE_BYTES["splat"],
+    }
+    achieved = alg_bytes[dom] / (cms[dom] * 1e-3) * 1e-9 if cms[dom] > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": pt_config_dict(args),
+        "rays_per_sample": {"closest": st["rays_closest"] / st["samples"], "shadow_slots": st["rays_shadow"] / st["samples"],
+                            "live_closest": prof["live_closest"] / prof["samples"], "live_shadow": prof["live_shadow"] / prof["samples"]},
+        "mrays_s_live": (prof["live_closest"] + prof["live_shadow"]) / prof["samples"] * value,
+        "film_check": {"weight_sum": wsum, "mean_rgb": mean_rgb},
+        "gpu_launches": int(launches),
+        "roofline": {
+            "bound": "hbm", "kernel": "%s kernels of one pass" % names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "launch_ms": cms[dom] / max(1, prof["class_launches"][dom]),
+            "class_ms_per_pass": dict(zip(names, cms)), "class_launches_per_pass": dict(zip(names, prof["class_launches"][:6])),
+            "class_algorithmic_GB": {names[k]: alg_bytes[k] * 1e-9 for k in range(6)},
+            "pass_ms_profiled": sum(cms),
+            "note": "algorithmic bytes: traversal = 48 B per ray slot (32 B ray in + 16 B hit out) + 80 B per BVH8 node visited + 48 B per "
+                    "triangle tested; shading = SoA path state read + written per stage (DESIGN.md section 5)",
+        },
+    }
+    if e2e:
+        line["e2e"] = {"value": n * world * e2e["steps"] / (e2e_ms * 1e-3) * 1e-6, "unit": UNIT, "h2d_bytes_per_step": e2e["h2d"],
+                       "d2h_bytes_per_step": e2e["d2h"], "steps": e2e["steps"], "timing": "host wall clock around the calls (max over ranks)",
+                       "api": "Interface.upload() [host geometry + scene -> device, BVH8 build] + render_pass() + read_film() [film -> host]"}
+    if world == 1 and not args.no_cpu_baseline:
+        r = reference_pt(argparse.Namespace(**{**vars(args), "steps": 2, "warmup": 1}))
+        line["cpu_baseline"] = ({"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "reference", "sample": r["sample"]}
+                                if "value" in r else {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": r["unavailable"]})
+    yi.clearAll()
+    return line
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
-    else:
-        run_b200_arm(args)
+        return
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- this back end has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    env = {"torch": torch, "dist": dist, "world": world, "rank": rank, "local": local, "dev": dev, "barrier": barrier,
+           "sampler": ClockSampler(local) if rank == 0 else None}
+    line = pt_arm(args, env)
+    rb = None if args.no_raybatch else raybatch_arm(args, env)
+    if rank == 0:
+        if rb is not None:
+            line["raybatch"] = rb
+            line["gpu_launches"] += rb.get("gpu_launches", 0)
+        line["clocks"] = env["sampler"].finish()
+        print(json.dumps(line))
+        sys.stdout.flush()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -188,7 +188,8 @@ typedef struct y4gpu_pt_params
 	uint32_t base_sampling_offset;                      /* adv_base_sampling_offset + 100000 * adv_computer_node */
 	uint32_t rr_seed;             /* seed of the per-path Russian-roulette hash (the reference uses rand()) */
 	uint32_t wave_size;           /* pixel-samples processed per wavefront (0 = default 2^21) */
-	int32_t reserved[7];
+	int32_t profile;              /* 1: time every kernel class with CUDA events and count BVH visits (slower; for the roofline) */
+	int32_t reserved[6];
 } y4gpu_pt_params;
 
 typedef struct y4gpu_pt_stats
@@ -197,6 +198,12 @@ typedef struct y4gpu_pt_stats
 	uint64_t rays_closest, rays_shadow;
 	uint64_t kernel_launches;     /* kernels launched by the last pass */
 	double pass_ms;               /* device time of the last pass (CUDA events) */
+	/* filled only when y4gpu_pt_params.profile != 0 */
+	double class_ms[8];           /* 0 fill+camera rays, 1 closest-hit traversal, 2 shadow traversal, 3 hit/bounce shading,
+	                                 4 light sampling + shadow resolve, 5 film splat */
+	uint64_t class_launches[8];
+	uint64_t nodes_closest, tris_closest, nodes_shadow, tris_shadow;   /* BVH8 nodes visited / triangles tested */
+	uint64_t live_closest, live_shadow;                                /* rays with a non-empty interval */
 	uint64_t reserved[4];
 } y4gpu_pt_stats;
 

@@ -63,12 +63,15 @@ class PtParams(C.Structure):
                 ("aa_sample_multiplier_factor", C.c_float), ("aa_light_sample_multiplier_factor", C.c_float),
                 ("aa_pixelwidth", C.c_float), ("aa_clamp_samples", C.c_float), ("filter_type", C.c_int32),
                 ("shadow_bias_auto", C.c_int32), ("shadow_bias", C.c_float), ("min_raydist_auto", C.c_int32), ("min_raydist", C.c_float),
-                ("base_sampling_offset", C.c_uint32), ("rr_seed", C.c_uint32), ("wave_size", C.c_uint32), ("reserved", C.c_int32 * 7)]  # fmt: skip
+                ("base_sampling_offset", C.c_uint32), ("rr_seed", C.c_uint32), ("wave_size", C.c_uint32), ("profile", C.c_int32),
+                ("reserved", C.c_int32 * 6)]  # fmt: skip
 
 
 class PtStats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64), ("kernel_launches", C.c_uint64),
-                ("pass_ms", C.c_double), ("reserved", C.c_uint64 * 4)]  # fmt: skip
+                ("pass_ms", C.c_double), ("class_ms", C.c_double * 8), ("class_launches", C.c_uint64 * 8),
+                ("nodes_closest", C.c_uint64), ("tris_closest", C.c_uint64), ("nodes_shadow", C.c_uint64), ("tris_shadow", C.c_uint64),
+                ("live_closest", C.c_uint64), ("live_shadow", C.c_uint64), ("reserved", C.c_uint64 * 4)]  # fmt: skip
 
 
 MAT_SHINYDIFFUSE, MAT_LIGHT = 0, 1

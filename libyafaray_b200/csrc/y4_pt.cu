@@ -25,6 +25,7 @@ struct Y4Pt
 	void *wave_mem = nullptr;
 	uint32_t *d_pixel_list = nullptr; uint64_t pixel_list_cap = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	std::vector<cudaEvent_t> prof_events;     // profile mode: one event after every launch
 	y4gpu_pt_stats stats = {};
 };
 
@@ -126,6 +127,7 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); cudaFree(pt->d_pixel_list);
 	if(pt->ev0) cudaEventDestroy(pt->ev0);
 	if(pt->ev1) cudaEventDestroy(pt->ev1);
+	for(cudaEvent_t e : pt->prof_events) cudaEventDestroy(e);
 	delete pt;
 	ctx->pt = nullptr;
 }
@@ -312,42 +314,70 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	{ const int rc = pt_alloc_wave(ctx, pt, wave_size); if(rc) return rc; }
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass_number;
 	const Y4PtScene *dsc = pt->d_scene;
-#define Y4_PT_LAUNCH(kernel, ...) do { kernel<<<grid, kPtThreads, 0, st>>>(__VA_ARGS__); ++own_launches; } while(0)
-#define Y4_PT_TRACE(kind, rays, count, hits) do { const int rc_ = y4_launch_trace(ctx, kind, false, rays, count, hits); if(rc_) return rc_; } while(0)
+	// profile mode: an event after every launch attributes device time to kernel classes; traversal runs counted
+	const bool prof = pt->params.profile != 0;
+	std::vector<int> prof_cls;
+	unsigned long long visits[2][3] = {{0, 0, 0}, {0, 0, 0}};
+	auto mark = [&](int cls) -> int
+	{
+		if(!prof) return Y4GPU_OK;
+		if(prof_cls.size() >= pt->prof_events.size()) { cudaEvent_t e; Y4_CUDA(ctx, cudaEventCreate(&e)); pt->prof_events.push_back(e); }
+		Y4_CUDA(ctx, cudaEventRecord(pt->prof_events[prof_cls.size()], st));
+		prof_cls.push_back(cls);
+		return Y4GPU_OK;
+	};
+	auto trace = [&](int kind, const Y4Ray *rays, uint64_t count, Y4Hit *hits) -> int
+	{
+		int rc_ = y4_launch_trace(ctx, kind, prof, rays, count, hits);
+		if(rc_) return rc_;
+		if(prof)
+		{
+			if((rc_ = mark(kind == Y4_TRACE_CLOSEST ? 1 : 2))) return rc_;
+			unsigned long long v[3];
+			Y4_CUDA(ctx, cudaMemcpyAsync(v, ctx->d_visit_counters, sizeof(v), cudaMemcpyDeviceToHost, st));
+			Y4_CUDA(ctx, cudaStreamSynchronize(st));
+			for(int q = 0; q < 3; ++q) visits[kind == Y4_TRACE_CLOSEST ? 0 : 1][q] += v[q];
+			if((rc_ = mark(-1))) return rc_;     // restart the clock after the read-back
+		}
+		return Y4GPU_OK;
+	};
+	{ const int rc_ = mark(-1); if(rc_) return rc_; }
+#define Y4_PT_LAUNCH(cls, kernel, ...) do { kernel<<<grid, kPtThreads, 0, st>>>(__VA_ARGS__); ++own_launches; const int rc_ = mark(cls); if(rc_) return rc_; } while(0)
+#define Y4_PT_TRACE(kind, rays, count, hits) do { const int rc_ = trace(kind, rays, count, hits); if(rc_) return rc_; } while(0)
 	for(uint64_t first = 0; first < total; first += wave_size)
 	{
 		Y4PtWave W = pt->wave;
 		W.n = (uint32_t) ((total - first) < wave_size ? (total - first) : wave_size);
 		const int grid = pt_grid(ctx, W.n);
-		Y4_PT_LAUNCH(k_pt_fill, W, d_list, first, ns_local, shard_index, shard_count);
-		Y4_PT_LAUNCH(k_pt_gen, dsc, W, ps);
+		Y4_PT_LAUNCH(0, k_pt_fill, W, d_list, first, ns_local, shard_index, shard_count);
+		Y4_PT_LAUNCH(0, k_pt_gen, dsc, W, ps);
 		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.n, W.hit); rays_closest += W.n;
-		Y4_PT_LAUNCH(k_pt_primary, dsc, W);
+		Y4_PT_LAUNCH(3, k_pt_primary, dsc, W);
 		for(int l = 0; l < sc.n_lights; ++l)
 		{
 			const int ns = y4_light_num_samples(sc, sc.lights[l]);
 			for(int k = 0; k < ns; ++k)
 			{
-				Y4_PT_LAUNCH(k_pt_direct, dsc, W, ps, 1, l, k);
+				Y4_PT_LAUNCH(4, k_pt_direct, dsc, W, ps, 1, l, k);
 				Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, 2ull * W.n, W.shit); rays_shadow += 2ull * W.n;
-				Y4_PT_LAUNCH(k_pt_direct_resolve, dsc, W, 1, l, k);
+				Y4_PT_LAUNCH(4, k_pt_direct_resolve, dsc, W, 1, l, k);
 			}
 		}
 		for(int sub = 0; sub < sc.n_paths; ++sub)
 			for(int depth = 0; depth < sc.bounces; ++depth)
 			{
-				Y4_PT_LAUNCH(k_pt_bounce_sample, dsc, W, ps, depth, sub);
+				Y4_PT_LAUNCH(3, k_pt_bounce_sample, dsc, W, ps, depth, sub);
 				Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.n, W.hit); rays_closest += W.n;
-				Y4_PT_LAUNCH(k_pt_bounce_hit, dsc, W, ps, depth, sub);
+				Y4_PT_LAUNCH(3, k_pt_bounce_hit, dsc, W, ps, depth, sub);
 				if(sc.n_lights == 0) continue;
 				for(int k = 0; k < pt->max_light_samples; ++k)
 				{
-					Y4_PT_LAUNCH(k_pt_direct, dsc, W, ps, 0, -1, k);
+					Y4_PT_LAUNCH(4, k_pt_direct, dsc, W, ps, 0, -1, k);
 					Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, 2ull * W.n, W.shit); rays_shadow += 2ull * W.n;
-					Y4_PT_LAUNCH(k_pt_direct_resolve, dsc, W, 0, -1, k);
+					Y4_PT_LAUNCH(4, k_pt_direct_resolve, dsc, W, 0, -1, k);
 				}
 			}
-		Y4_PT_LAUNCH(k_pt_splat, dsc, W, ps, pt->d_film_w, pt->d_film_rgba);
+		Y4_PT_LAUNCH(5, k_pt_splat, dsc, W, ps, pt->d_film_w, pt->d_film_rgba);
 		Y4_CUDA(ctx, cudaGetLastError());
 	}
 #undef Y4_PT_LAUNCH
@@ -357,5 +387,19 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	pt->stats.samples = total;
 	pt->stats.rays_closest = rays_closest; pt->stats.rays_shadow = rays_shadow;
 	pt->stats.kernel_launches = ctx->stats.kernel_launches - launches0;
+	for(int q = 0; q < 8; ++q) { pt->stats.class_ms[q] = 0.; pt->stats.class_launches[q] = 0; }
+	if(prof)
+	{
+		Y4_CUDA(ctx, cudaStreamSynchronize(st));
+		for(size_t e = 1; e < prof_cls.size(); ++e)
+		{
+			if(prof_cls[e] < 0) continue;
+			float ms = 0.f;
+			Y4_CUDA(ctx, cudaEventElapsedTime(&ms, pt->prof_events[e - 1], pt->prof_events[e]));
+			pt->stats.class_ms[prof_cls[e]] += ms; pt->stats.class_launches[prof_cls[e]]++;
+		}
+	}
+	pt->stats.nodes_closest = visits[0][0]; pt->stats.tris_closest = visits[0][1]; pt->stats.live_closest = visits[0][2];
+	pt->stats.nodes_shadow = visits[1][0]; pt->stats.tris_shadow = visits[1][1]; pt->stats.live_shadow = visits[1][2];
 	return Y4GPU_OK;
 }

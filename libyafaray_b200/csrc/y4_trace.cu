@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 	const uint32_t lt_mask = (1u << lane) - 1u;
 	const uint32_t vis_bit = KIND == Y4_TRACE_CLOSEST ? Y4_TRI_VIS_CLOSEST : Y4_TRI_VIS_SHADOW;
 	uint2 stack[Y4_STACK_SIZE];
-	unsigned long long my_nodes = 0, my_tris = 0;
+	unsigned long long my_nodes = 0, my_tris = 0, my_live = 0;
 	bool have = false, exhausted = false;
 	uint64_t ray_i = 0;
 	Y4RayCtx rc = y4_ray_ctx(v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 1.f));
@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 				// virtual parent of the root: child_base 0, imask = slot 0, hit bit at slot 0's priority
 				// empty scene or empty interval (the path tracer parks finished paths as null rays): nothing to visit
 				ngroup.x = 0u; ngroup.y = (bvh.n_tris && pr.t_hi > pr.t_lo) ? ((1u << (24u + rc.oct_inv)) | 1u) : 0u;
+				if(COUNT && ngroup.y) my_live++;
 			}
 		}
 		if(!__any_sync(0xffffffffu, have)) break;
@@ -135,8 +136,9 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 		{
 			my_nodes += __shfl_xor_sync(0xffffffffu, my_nodes, o);
 			my_tris += __shfl_xor_sync(0xffffffffu, my_tris, o);
+			my_live += __shfl_xor_sync(0xffffffffu, my_live, o);
 		}
-		if(lane == 0) { atomicAdd(visit, my_nodes); atomicAdd(visit + 1, my_tris); }
+		if(lane == 0) { atomicAdd(visit, my_nodes); atomicAdd(visit + 1, my_tris); atomicAdd(visit + 2, my_live); }
 	}
 }
 
@@ -206,7 +208,7 @@ int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays,
 	if(n == 0) return Y4GPU_OK;
 	cudaStream_t st = ctx->stream;
 	Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_work_counter, 0, sizeof(unsigned long long), st));
-	if(counted) Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_visit_counters, 0, 2 * sizeof(unsigned long long), st));
+	if(counted) Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_visit_counters, 0, 3 * sizeof(unsigned long long), st));
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
 	int rc;
 	if(kind == Y4_TRACE_CLOSEST) rc = counted ? launch<Y4_TRACE_CLOSEST, true>(ctx, d_rays, n, d_out) : launch<Y4_TRACE_CLOSEST, false>(ctx, d_rays, n, d_out);

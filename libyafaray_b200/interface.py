@@ -335,6 +335,7 @@ class Interface:
         pr.base_sampling_offset = (int(rp.get("adv_base_sampling_offset", 0)) + 100000 * int(rp.get("adv_computer_node", 0))) & 0xFFFFFFFF
         pr.rr_seed = int(rp.get("b200_rr_seed", 0x5EED)) & 0xFFFFFFFF
         pr.wave_size = int(rp.get("b200_wave_size", 0))
+        pr.profile = int(rp.get("b200_profile", 0))
         return {"tris": T, "flags": F, "normals": N, "cam": cam, "mats": mats, "n_mat": len(mat_names), "lights": lights,
                 "n_light": len(light_names), "params": pr}
 
@@ -389,13 +390,20 @@ class Interface:
         self.last_stats = stats
         return self.read_image()
 
-    def _add_stats(self, acc):
+    def pass_stats(self) -> dict:
+        """y4gpu_pt_stats of the last pass (synchronises)."""
         self.accelerator.synchronize()
         s = _lib.PtStats()
         L, ctx = self.accelerator._L, self.accelerator.ctx
         _lib.check(ctx, L.y4gpu_pt_get_stats(ctx, C.byref(s)), "y4gpu_pt_get_stats")
+        d = {k: getattr(s, k) for k, _ in s._fields_ if k not in ("reserved", "class_ms", "class_launches")}
+        d["class_ms"], d["class_launches"] = list(s.class_ms), list(s.class_launches)
+        return d
+
+    def _add_stats(self, acc):
+        s = self.pass_stats()
         for k in acc:
-            acc[k] += getattr(s, k)
+            acc[k] += s[k]
 
     def read_film(self):
         """-> (weights [h, w], rgba [h, w, 4]) as accumulated (ImageFilm::weights_ and the Combined layer)."""

@@ -31,7 +31,7 @@ static void trace(const Y4Bvh8 &bvh, int kind, const Y4Ray *rays, size_t n, Y4Hi
 
 extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material *mats, uint32_t n_mat, const y4gpu_pt_light *lights, uint32_t n_light,
                              const y4gpu_pt_params *params, const float *verts, const uint32_t *flags, int n_tri, const float *normals,
-                             int n_samples, int offset, int aa_pass, float *film_w, float *film_rgba)
+                             int n_samples, int offset, int aa_pass, int shard_index, int shard_count, float *film_w, float *film_rgba)
 {
 	EmuBvh b;
 	emu_build(verts, flags, n_tri, 1, b);
@@ -58,7 +58,10 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	sc.mats = hm.data(); sc.verts = verts; sc.tri_flags = flags; sc.normals = normals;
 	sc.lds.sigma = fh.sigma.data(); sc.lds.offset = fh.offset; sc.lds.prime = fh.prime; sc.lds.inv_prime = fh.inv_prime;
 
-	const uint32_t n = (uint32_t) sc.width * sc.height * (uint32_t) n_samples;
+	// same pixel-sample enumeration as k_pt_fill (y4_pt.cu)
+	const uint32_t ns_local = shard_index < n_samples ? (uint32_t) ((n_samples - shard_index + shard_count - 1) / shard_count) : 0u;
+	const uint32_t n = (uint32_t) sc.width * sc.height * ns_local;
+	if(n == 0) return 0;
 	std::vector<uint32_t> pix(n), samp(n), fl(n), lnum(n);
 	std::vector<float> col(4ull * n), pcol(4ull * n), thr(4ull * n), lcol(4ull * n), acc_a(4ull * n), acc_b(4ull * n), scontrib(8ull * n);
 	std::vector<Y4Ray> ray(n), sray(2ull * n);
@@ -68,7 +71,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	W.col = col.data(); W.pcol = pcol.data(); W.thr = thr.data(); W.lcol = lcol.data(); W.acc_a = acc_a.data(); W.acc_b = acc_b.data();
 	W.ray = ray.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = scontrib.data();
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
-	for(uint32_t i = 0; i < n; ++i) { pix[i] = i / (uint32_t) n_samples; samp[i] = i % (uint32_t) n_samples; }
+	for(uint32_t i = 0; i < n; ++i) { pix[i] = i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
 	for(uint32_t i = 0; i < n; ++i) y4_pt_gen(sc, W, ps, i);
 	trace(bvh, Y4_TRACE_CLOSEST, W.ray, n, W.hit);
 	for(uint32_t i = 0; i < n; ++i) y4_pt_primary(sc, W, i);

@@ -90,7 +90,7 @@ from refserver import RefServer  # noqa: E402,F401
 from refserver import ScriptRecorder, ref_render  # noqa: E402,F401
 
 
-def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0):
+def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0, shard_index=0, shard_count=1):
     """CPU emulation of the wavefront path tracer stages on an Interface.assemble() result -> (weights, rgba)."""
     import ctypes as C
 
@@ -102,7 +102,7 @@ def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0):
     f.restype = C.c_int
     nptr = a["normals"].ctypes.data_as(C.c_void_p) if a["normals"] is not None else None
     rc = f(C.byref(a["cam"]), a["mats"], C.c_uint32(a["n_mat"]), a["lights"], C.c_uint32(a["n_light"]), C.byref(pr), _p(a["tris"]), _p(a["flags"]),
-           C.c_int(len(a["tris"])), nptr, C.c_int(n_samples), C.c_int(offset), C.c_int(aa_pass), _p(w), _p(rgba))
+           C.c_int(len(a["tris"])), nptr, C.c_int(n_samples), C.c_int(offset), C.c_int(aa_pass), C.c_int(shard_index), C.c_int(shard_count), _p(w), _p(rgba))
     assert rc == 0
     return w, rgba
 
