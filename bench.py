@@ -476,14 +476,14 @@ def run_reference_arm(args):
     r = reference_pt(args)
     if "unavailable" in r:
         line["unavailable"] = r["unavailable"]
-        print(json.dumps(line))
+        print_json(line)
         return
     line.update({"value": r["value"], "ms_per_step": r["ms_per_step"],
                  "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "reference", "sample": r["sample"]},
                  "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0})
     if not args.no_raybatch:
         line["raybatch"] = reference_raybatch(args)
-    print(json.dumps(line))
+    print_json(line)
 
 
 # algorithmic bytes per pixel-sample moved by the shading stages: SoA state read + written
@@ -629,6 +629,14 @@ def pt_arm(args, env):
 
 def main():
     args = parse_args()
+    # stdout carries exactly ONE JSON line: anything libraries print to fd 1 (e.g. NCCL's version banner) goes to stderr
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
+    global print_json
+
+    def print_json(obj):
+        os.write(out_fd, (json.dumps(obj) + "\n").encode())
+
     if args.impl == "reference":
         run_reference_arm(args)
         return
@@ -659,8 +667,7 @@ def main():
             line["raybatch"] = rb
             line["gpu_launches"] += rb.get("gpu_launches", 0)
         line["clocks"] = env["sampler"].finish()
-        print(json.dumps(line))
-        sys.stdout.flush()
+        print_json(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
