@@ -23,6 +23,12 @@ struct Y4Pt
 	uint32_t cap = 0;
 	Y4PtWave wave = {};
 	void *wave_mem = nullptr;
+	uint32_t *q_hit0 = nullptr, *q_path[2] = {nullptr, nullptr}, *q_shadow = nullptr;   // index queues (in wave_mem)
+	// per-launch counters: 64-bit slots, zeroed once per pass; a queue length is the low word of its slot
+	unsigned long long *d_counters = nullptr, *h_counters = nullptr; size_t counters_cap = 0;
+	std::vector<std::pair<uint32_t, int>> counter_kinds;      // (slot, 0 closest queue / 1 shadow queue) of the last pass
+	uint64_t dense_closest = 0;
+	bool counters_read = true;
 	uint32_t *d_pixel_list = nullptr; uint64_t pixel_list_cap = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	std::vector<cudaEvent_t> prof_events;     // profile mode: one event after every launch
@@ -31,12 +37,25 @@ struct Y4Pt
 
 #include "y4_pt_host.h"
 
-// ---- kernels: one thread per pixel-sample of the wave, grid-stride ----------------------------------
+// ---- kernels -------------------------------------------------------------------------------------------
+// Dense kernels (camera rays, splat) run one thread per pixel-sample of the wave.  Stage kernels run one
+// thread per entry of a device-built index queue (the live paths of the wavefront) and append to the
+// shadow-ray queue and to the stage's output path queue with one atomic per warp and queue.
 namespace {
 
 constexpr int kPtThreads = 256;
 
-__global__ void __launch_bounds__(kPtThreads) k_pt_fill(Y4PtWave W, const uint32_t *__restrict__ pixel_list, uint64_t first, uint32_t ns_local, int shard_index, int shard_count)
+enum { kStPrimary, kStDirectStep, kStStart, kStVertex, kStExtend };
+struct StageArgs { int all_lights, l_prev, k_prev, l, k, depth, sub; };
+struct StageQueues
+{
+	const uint32_t *in_q, *in_count;     // null: dense over the wave
+	uint32_t *out_q, *out_count;         // paths that continue
+	uint32_t *sh_q, *sh_count;           // shadow rays to trace: slot index into W.sray / W.shit
+};
+
+__global__ void __launch_bounds__(kPtThreads) k_pt_gen(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, const uint32_t *__restrict__ pixel_list,
+                                                        uint64_t first, uint32_t ns_local, int shard_index, int shard_count)
 {
 	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x)
 	{
@@ -44,32 +63,55 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_fill(Y4PtWave W, const uint32
 		const uint64_t slot = g / ns_local;
 		W.pix[i] = pixel_list ? pixel_list[slot] : (uint32_t) slot;
 		W.samp[i] = (uint32_t) shard_index + (uint32_t) (g % ns_local) * (uint32_t) shard_count;
+		y4_pt_gen(*sc, W, ps, i);
 	}
 }
-__global__ void __launch_bounds__(kPtThreads) k_pt_gen(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps)
+
+template<int STAGE>
+__global__ void __launch_bounds__(kPtThreads) k_pt_stage(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, StageArgs a, StageQueues Q)
 {
-	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_gen(*sc, W, ps, i);
+	const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+	const uint32_t count = Q.in_q ? *Q.in_count : W.n;
+	const uint32_t stride = gridDim.x * blockDim.x;
+	for(uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < count; base += stride)
+	{
+		const uint32_t q = base + lane;
+		uint32_t push = 0u, i = 0u;
+		if(q < count)
+		{
+			i = Q.in_q ? Q.in_q[q] : q;
+			if(STAGE == kStPrimary) push = y4_stage_primary(*sc, W, ps, i, a.l);
+			else if(STAGE == kStDirectStep) push = y4_stage_direct_step(*sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
+			else if(STAGE == kStStart) push = y4_stage_start(*sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
+			else if(STAGE == kStVertex) push = y4_stage_vertex(*sc, W, ps, i, a.depth, a.sub);
+			else push = y4_stage_extend(*sc, W, ps, i, a.depth, a.sub, a.k_prev);
+		}
+		if(STAGE == kStPrimary || STAGE == kStDirectStep || STAGE == kStVertex)
+		{
+			const uint32_t m0 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S0), m1 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S1);
+			if(m0 | m1)
+			{
+				uint32_t at = 0u;
+				if(lane == 0) at = atomicAdd(Q.sh_count, (uint32_t) (__popc(m0) + __popc(m1)));
+				at = __shfl_sync(0xffffffffu, at, 0);
+				if(push & Y4_PUSH_S0) Q.sh_q[at + __popc(m0 & lt_mask)] = i;
+				if(push & Y4_PUSH_S1) Q.sh_q[at + __popc(m0) + __popc(m1 & lt_mask)] = W.n + i;
+			}
+		}
+		if(STAGE == kStPrimary || STAGE == kStStart || STAGE == kStExtend)
+		{
+			const uint32_t mp = __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH);
+			if(mp)
+			{
+				uint32_t at = 0u;
+				if(lane == 0) at = atomicAdd(Q.out_count, (uint32_t) __popc(mp));
+				at = __shfl_sync(0xffffffffu, at, 0);
+				if(push & Y4_PUSH_PATH) Q.out_q[at + __popc(mp & lt_mask)] = i;
+			}
+		}
+	}
 }
-__global__ void __launch_bounds__(kPtThreads) k_pt_primary(const Y4PtScene *__restrict__ sc, Y4PtWave W)
-{
-	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_primary(*sc, W, i);
-}
-__global__ void __launch_bounds__(kPtThreads) k_pt_direct(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, int all_lights, int light, int k)
-{
-	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_direct(*sc, W, ps, i, all_lights != 0, light, k);
-}
-__global__ void __launch_bounds__(kPtThreads) k_pt_direct_resolve(const Y4PtScene *__restrict__ sc, Y4PtWave W, int all_lights, int light, int k)
-{
-	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_direct_resolve(*sc, W, i, all_lights != 0, light, k);
-}
-__global__ void __launch_bounds__(kPtThreads) k_pt_bounce_sample(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, int depth, int sub)
-{
-	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_bounce_sample(*sc, W, ps, i, depth, sub);
-}
-__global__ void __launch_bounds__(kPtThreads) k_pt_bounce_hit(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, int depth, int sub)
-{
-	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_bounce_hit(*sc, W, ps, i, depth, sub);
-}
+
 __global__ void __launch_bounds__(kPtThreads) k_pt_splat(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, float *film_w, float *film_rgba)
 {
 	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_finish_splat(*sc, W, ps, i, film_w, film_rgba);
@@ -92,7 +134,8 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt *pt, uint32_t cap)
 	if(cap <= pt->cap) return Y4GPU_OK;
 	pt_free_wave(pt);
 	const size_t n = cap;
-	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 32 + 16 + 16 /*ray hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/) + 256;
+	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 32 + 16 + 16 /*ray hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/
+	                          + 5 * 4 /*queues*/) + 512;
 	Y4_CUDA(ctx, cudaMalloc(&pt->wave_mem, bytes));
 	char *p = (char *) pt->wave_mem;
 	auto take = [&](size_t b) { char *r = p; p += (b + 15) & ~(size_t) 15; return (void *) r; };
@@ -102,6 +145,7 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt *pt, uint32_t cap)
 	W.ray = (Y4Ray *) take(n * 32); W.hit = (Y4Hit *) take(n * 16); W.hit0 = (Y4Hit *) take(n * 16);
 	W.sray = (Y4Ray *) take(2 * n * 32); W.shit = (Y4Hit *) take(2 * n * 16); W.scontrib = (float *) take(2 * n * 16);
 	W.pix = (uint32_t *) take(n * 4); W.samp = (uint32_t *) take(n * 4); W.flags = (uint32_t *) take(n * 4); W.lnum = (uint32_t *) take(n * 4);
+	pt->q_hit0 = (uint32_t *) take(n * 4); pt->q_path[0] = (uint32_t *) take(n * 4); pt->q_path[1] = (uint32_t *) take(n * 4); pt->q_shadow = (uint32_t *) take(2 * n * 4);
 	pt->cap = cap;
 	return Y4GPU_OK;
 }
@@ -125,6 +169,7 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	cudaFree(pt->d_scene); cudaFree(pt->d_mats); cudaFree(pt->d_normals);
 	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime);
 	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); cudaFree(pt->d_pixel_list);
+	cudaFree(pt->d_counters); cudaFreeHost(pt->h_counters);
 	if(pt->ev0) cudaEventDestroy(pt->ev0);
 	if(pt->ev1) cudaEventDestroy(pt->ev1);
 	for(cudaEvent_t e : pt->prof_events) cudaEventDestroy(e);
@@ -257,10 +302,27 @@ int y4gpu_pt_read_film(y4gpu_ctx *ctx, float *weights, float *rgba)
 int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out)
 {
 	if(!ctx || !out || !ctx->pt) return Y4GPU_ERR_ARG;
-	*out = ctx->pt->stats;
+	Y4Pt *pt = ctx->pt;
 	float ms = 0.f;
-	if(ctx->pt->ev1 && cudaEventQuery(ctx->pt->ev1) == cudaSuccess && cudaEventElapsedTime(&ms, ctx->pt->ev0, ctx->pt->ev1) == cudaSuccess) out->pass_ms = ms;
+	if(pt->ev1 && cudaEventSynchronize(pt->ev1) == cudaSuccess)
+	{
+		if(cudaEventElapsedTime(&ms, pt->ev0, pt->ev1) == cudaSuccess) pt->stats.pass_ms = ms;
+		if(!pt->counters_read)
+		{
+			// queue lengths of the pass (copied to pinned memory before ev1): rays actually traced
+			uint64_t rc = pt->dense_closest, rs = 0;
+			for(const auto &ck : pt->counter_kinds) (ck.second ? rs : rc) += (uint32_t) pt->h_counters[ck.first];
+			pt->stats.rays_closest = rc; pt->stats.rays_shadow = rs;
+			if(pt->params.profile)
+			{
+				pt->stats.nodes_closest = pt->h_counters[0]; pt->stats.tris_closest = pt->h_counters[1]; pt->stats.live_closest = pt->h_counters[2];
+				pt->stats.nodes_shadow = pt->h_counters[3]; pt->stats.tris_shadow = pt->h_counters[4]; pt->stats.live_shadow = pt->h_counters[5];
+			}
+			pt->counters_read = true;
+		}
+	}
 	else cudaGetLastError();
+	*out = pt->stats;
 	return Y4GPU_OK;
 }
 
@@ -278,7 +340,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	cudaStream_t st = ctx->stream;
 	Y4PtScene &sc = pt->h_scene;
 	const uint64_t launches0 = ctx->stats.kernel_launches;
-	uint64_t own_launches = 0, rays_closest = 0, rays_shadow = 0;
+	uint64_t own_launches = 0;
 	// per-pass light sample multiplier (integrator_tiled.cc:189-191: multiplied once per additional pass)
 	float mult = 1.f;
 	for(int p = 0; p < aa_pass_number; ++p) mult *= pt->params.aa_light_sample_multiplier_factor > 0.f ? pt->params.aa_light_sample_multiplier_factor : 1.f;
@@ -309,15 +371,39 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 			d_list = pt->d_pixel_list;
 		}
 	}
-	uint32_t wave_size = pt->params.wave_size ? pt->params.wave_size : (1u << 21);
+	uint32_t wave_size = pt->params.wave_size ? pt->params.wave_size : (1u << 22);
 	if(total < wave_size) wave_size = (uint32_t) (total ? total : 1);
 	{ const int rc = pt_alloc_wave(ctx, pt, wave_size); if(rc) return rc; }
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass_number;
 	const Y4PtScene *dsc = pt->d_scene;
+	// the (light, sample) sequence of estimateAllDirectLight at the camera hit
+	std::vector<std::pair<int, int>> all_lk;
+	for(int l = 0; l < sc.n_lights; ++l)
+		for(int k = 0, ns = y4_light_num_samples(sc, sc.lights[l]); k < ns; ++k) all_lk.push_back(std::make_pair(l, k));
+	const int max_ls = pt->max_light_samples;
+	// counter slots: [0..5] traversal visit counters (profile mode), then one per queue / trace launch
+	const uint64_t n_waves = total ? (total + wave_size - 1) / wave_size : 0;
+	const size_t per_wave = 4 + 2 * all_lk.size() + (size_t) sc.n_paths * (2 + (size_t) sc.bounces * (4 + 2 * (size_t) max_ls));
+	const size_t need = 8 + n_waves * per_wave;
+	if(need > pt->counters_cap)
+	{
+		cudaFree(pt->d_counters); cudaFreeHost(pt->h_counters); pt->d_counters = nullptr; pt->h_counters = nullptr; pt->counters_cap = 0;
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_counters, need * sizeof(unsigned long long)));
+		Y4_CUDA(ctx, cudaHostAlloc(&pt->h_counters, need * sizeof(unsigned long long), cudaHostAllocDefault));
+		pt->counters_cap = need;
+	}
+	Y4_CUDA(ctx, cudaMemsetAsync(pt->d_counters, 0, need * sizeof(unsigned long long), st));
+	pt->counter_kinds.clear(); pt->dense_closest = 0;
+	size_t next_slot = 8;
+	auto new_slot = [&]() -> unsigned long long * { return pt->d_counters + (next_slot < need ? next_slot++ : need - 1); };
+	auto new_queue_count = [&](int kind) -> uint32_t *
+	{
+		if(kind >= 0) pt->counter_kinds.push_back(std::make_pair((uint32_t) next_slot, kind));
+		return reinterpret_cast<uint32_t *>(new_slot());
+	};
 	// profile mode: an event after every launch attributes device time to kernel classes; traversal runs counted
 	const bool prof = pt->params.profile != 0;
 	std::vector<int> prof_cls;
-	unsigned long long visits[2][3] = {{0, 0, 0}, {0, 0, 0}};
 	auto mark = [&](int cls) -> int
 	{
 		if(!prof) return Y4GPU_OK;
@@ -326,66 +412,75 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		prof_cls.push_back(cls);
 		return Y4GPU_OK;
 	};
-	auto trace = [&](int kind, const Y4Ray *rays, uint64_t count, Y4Hit *hits) -> int
-	{
-		int rc_ = y4_launch_trace(ctx, kind, prof, rays, count, hits);
-		if(rc_) return rc_;
-		if(prof)
-		{
-			if((rc_ = mark(kind == Y4_TRACE_CLOSEST ? 1 : 2))) return rc_;
-			unsigned long long v[3];
-			Y4_CUDA(ctx, cudaMemcpyAsync(v, ctx->d_visit_counters, sizeof(v), cudaMemcpyDeviceToHost, st));
-			Y4_CUDA(ctx, cudaStreamSynchronize(st));
-			for(int q = 0; q < 3; ++q) visits[kind == Y4_TRACE_CLOSEST ? 0 : 1][q] += v[q];
-			if((rc_ = mark(-1))) return rc_;     // restart the clock after the read-back
-		}
-		return Y4GPU_OK;
-	};
 	{ const int rc_ = mark(-1); if(rc_) return rc_; }
-#define Y4_PT_LAUNCH(cls, kernel, ...) do { kernel<<<grid, kPtThreads, 0, st>>>(__VA_ARGS__); ++own_launches; const int rc_ = mark(cls); if(rc_) return rc_; } while(0)
-#define Y4_PT_TRACE(kind, rays, count, hits) do { const int rc_ = trace(kind, rays, count, hits); if(rc_) return rc_; } while(0)
+#define Y4_PT_LAUNCH(cls, ...) do { __VA_ARGS__; ++own_launches; const int rc_ = mark(cls); if(rc_) return rc_; } while(0)
+#define Y4_PT_TRACE(kind, rays, hits, n_max, queue, count) do { \
+		int rc_ = y4_launch_trace_wave(ctx, kind, prof, rays, hits, n_max, queue, count, new_slot(), pt->d_counters + (kind == Y4_TRACE_CLOSEST ? 0 : 3)); \
+		if(rc_ || (rc_ = mark(kind == Y4_TRACE_CLOSEST ? 1 : 2))) return rc_; } while(0)
 	for(uint64_t first = 0; first < total; first += wave_size)
 	{
 		Y4PtWave W = pt->wave;
 		W.n = (uint32_t) ((total - first) < wave_size ? (total - first) : wave_size);
 		const int grid = pt_grid(ctx, W.n);
-		Y4_PT_LAUNCH(0, k_pt_fill, W, d_list, first, ns_local, shard_index, shard_count);
-		Y4_PT_LAUNCH(0, k_pt_gen, dsc, W, ps);
-		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.n, W.hit); rays_closest += W.n;
-		Y4_PT_LAUNCH(3, k_pt_primary, dsc, W);
-		for(int l = 0; l < sc.n_lights; ++l)
+		StageArgs a = {0, -1, -1, -1, -1, 0, 0};
+		StageQueues Q = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+		// camera rays -> closest hits -> camera-hit stage with the first light sample
+		Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, ns_local, shard_index, shard_count));
+		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, nullptr, nullptr); pt->dense_closest += W.n;
+		uint32_t *n_hit0 = new_queue_count(-1);
+		Q.out_q = pt->q_hit0; Q.out_count = n_hit0; Q.sh_q = pt->q_shadow; Q.sh_count = new_queue_count(1);
+		a.l = all_lk.empty() ? -1 : all_lk[0].first;
+		Y4_PT_LAUNCH(3, k_pt_stage<kStPrimary><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
+		for(size_t j = 0; j < all_lk.size(); ++j)
 		{
-			const int ns = y4_light_num_samples(sc, sc.lights[l]);
-			for(int k = 0; k < ns; ++k)
-			{
-				Y4_PT_LAUNCH(4, k_pt_direct, dsc, W, ps, 1, l, k);
-				Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, 2ull * W.n, W.shit); rays_shadow += 2ull * W.n;
-				Y4_PT_LAUNCH(4, k_pt_direct_resolve, dsc, W, 1, l, k);
-			}
+			Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
+			if(j + 1 == all_lk.size()) break;          // the last sample is resolved by the start stage
+			Q.in_q = pt->q_hit0; Q.in_count = n_hit0; Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
+			a.all_lights = 1; a.l_prev = all_lk[j].first; a.k_prev = all_lk[j].second; a.l = all_lk[j + 1].first; a.k = all_lk[j + 1].second;
+			Y4_PT_LAUNCH(4, k_pt_stage<kStDirectStep><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
 		}
 		for(int sub = 0; sub < sc.n_paths; ++sub)
+		{
+			int cur = 0;
+			uint32_t *n_cur = new_queue_count(0);
+			Q.in_q = pt->q_hit0; Q.in_count = n_hit0; Q.out_q = pt->q_path[cur]; Q.out_count = n_cur; Q.sh_q = pt->q_shadow; Q.sh_count = nullptr;
+			a.all_lights = 1; a.sub = sub; a.l_prev = (sub == 0 && !all_lk.empty()) ? all_lk.back().first : -1; a.k_prev = a.l_prev >= 0 ? all_lk.back().second : -1;
+			Y4_PT_LAUNCH(3, k_pt_stage<kStStart><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
 			for(int depth = 0; depth < sc.bounces; ++depth)
 			{
-				Y4_PT_LAUNCH(3, k_pt_bounce_sample, dsc, W, ps, depth, sub);
-				Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.n, W.hit); rays_closest += W.n;
-				Y4_PT_LAUNCH(3, k_pt_bounce_hit, dsc, W, ps, depth, sub);
-				if(sc.n_lights == 0) continue;
-				for(int k = 0; k < pt->max_light_samples; ++k)
+				Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, pt->q_path[cur], n_cur);
+				Q.in_q = pt->q_path[cur]; Q.in_count = n_cur; Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(sc.n_lights ? 1 : -1);
+				a.all_lights = 0; a.depth = depth; a.sub = sub;
+				Y4_PT_LAUNCH(3, k_pt_stage<kStVertex><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
+				if(sc.n_lights)
 				{
-					Y4_PT_LAUNCH(4, k_pt_direct, dsc, W, ps, 0, -1, k);
-					Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, 2ull * W.n, W.shit); rays_shadow += 2ull * W.n;
-					Y4_PT_LAUNCH(4, k_pt_direct_resolve, dsc, W, 0, -1, k);
+					Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
+					for(int k = 1; k < max_ls; ++k)
+					{
+						Q.sh_count = new_queue_count(1);
+						a.l_prev = -1; a.k_prev = k - 1; a.l = -1; a.k = k;
+						Y4_PT_LAUNCH(4, k_pt_stage<kStDirectStep><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
+						Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
+					}
 				}
+				uint32_t *n_next = new_queue_count(depth + 1 < sc.bounces ? 0 : -1);
+				Q.out_q = pt->q_path[cur ^ 1]; Q.out_count = n_next; Q.sh_count = nullptr;
+				a.k_prev = sc.n_lights ? max_ls - 1 : -1;
+				Y4_PT_LAUNCH(4, k_pt_stage<kStExtend><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
+				cur ^= 1; n_cur = n_next;
 			}
-		Y4_PT_LAUNCH(5, k_pt_splat, dsc, W, ps, pt->d_film_w, pt->d_film_rgba);
+		}
+		Y4_PT_LAUNCH(5, k_pt_splat<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, pt->d_film_w, pt->d_film_rgba));
 		Y4_CUDA(ctx, cudaGetLastError());
 	}
 #undef Y4_PT_LAUNCH
 #undef Y4_PT_TRACE
+	Y4_CUDA(ctx, cudaMemcpyAsync(pt->h_counters, pt->d_counters, need * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+	pt->counters_read = false;
 	Y4_CUDA(ctx, cudaEventRecord(pt->ev1, st));
 	ctx->stats.kernel_launches += own_launches;
 	pt->stats.samples = total;
-	pt->stats.rays_closest = rays_closest; pt->stats.rays_shadow = rays_shadow;
+	pt->stats.rays_closest = 0; pt->stats.rays_shadow = 0;
 	pt->stats.kernel_launches = ctx->stats.kernel_launches - launches0;
 	for(int q = 0; q < 8; ++q) { pt->stats.class_ms[q] = 0.; pt->stats.class_launches[q] = 0; }
 	if(prof)
@@ -399,7 +494,5 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 			pt->stats.class_ms[prof_cls[e]] += ms; pt->stats.class_launches[prof_cls[e]]++;
 		}
 	}
-	pt->stats.nodes_closest = visits[0][0]; pt->stats.tris_closest = visits[0][1]; pt->stats.live_closest = visits[0][2];
-	pt->stats.nodes_shadow = visits[1][0]; pt->stats.tris_shadow = visits[1][1]; pt->stats.live_shadow = visits[1][2];
 	return Y4GPU_OK;
 }

@@ -71,47 +71,58 @@ Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py)
 	return y4_mk_ray(cam.pos, tmin, d, tmax);
 }
 
-// ---- stage: camera rays ------------------------------------------------------------------------
-Y4_HD void y4_pt_gen(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
-{
-	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
-	W.ray[i] = y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy));
-	W.flags[i] = 0u;
-}
+// Elemental steps take the path's flag word in a register (`f`); the fused stage functions further
+// down load and store it once.  Shadow rays exist only for the slots whose Y4_PF_S0/S1 bit is set;
+// an untraced slot counts as unoccluded (no shadow casting, or an invalid sample with zero contribution).
+
+// ---- step: camera ray ---------------------------------------------------------------------------
 Y4_HD Y4Ray y4_primary_ray(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
 {
 	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
 	return y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy));
 }
+Y4_HD void y4_pt_gen(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
+{
+	W.ray[i] = y4_primary_ray(sc, W, ps, i);
+	W.flags[i] = 0u;
+}
 
-// ---- stage: camera-ray hit (integrate(), :126-171 up to the path loop) ---------------------------
-Y4_HD void y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i)
+struct Y4Vertex { Y4Surf sp; Y4PtMaterial m; V3 wo; };
+Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
+{
+	Y4Vertex v;
+	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
+	v.sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
+	v.m = sc.mats[v.sp.mat];
+	v.wo = xneg(d);
+	return v;
+}
+
+// ---- step: camera-ray hit (integrate(), :126-171 up to the path loop) -----------------------------
+// returns true and fills `vx` when the camera ray hit a surface
+Y4_HD bool y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t &f, Y4Vertex &vx)
 {
 	const Y4Hit h = W.hit[i];
-	const Y4Ray r = W.ray[i];
 	W.hit0[i] = h;
-	st3(W.pcol, i, c3f(0.f)); st3(W.acc_a, i, c3f(0.f)); st3(W.acc_b, i, c3f(0.f)); st3(W.lcol, i, c3f(0.f)); st3(W.thr, i, c3f(0.f));
 	if(h.prim < 0)
 	{
 		const bool transp = sc.transp_background != 0;      // ray_level == 0
 		st3(W.col, i, transp ? c3f(0.f) : sc.background);
 		W.col[4ull * i + 3] = transp ? 0.f : 1.f;
-		W.flags[i] = 0u;
-		return;
+		f = 0u;
+		return false;
 	}
-	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
-	const Y4Surf sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
-	const Y4PtMaterial m = sc.mats[sp.mat];
-	const V3 wo = xneg(d);
+	vx = y4_vertex(sc, W.ray[i], h);
 	C3 col = c3f(0.f);
-	if(m.bsdf_flags & Y4_BSDF_EMIT) col = cadd(col, y4_mat_emit(m, sp, wo));
+	if(vx.m.bsdf_flags & Y4_BSDF_EMIT) col = cadd(col, y4_mat_emit(vx.m, vx.sp, vx.wo));
 	st3(W.col, i, col);
 	W.col[4ull * i + 3] = 1.f;                                // recursiveRaytrace: alpha_count == 0 -> 1
-	uint32_t f = Y4_PF_HIT0;
-	if(m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
+	st3(W.pcol, i, c3f(0.f));
+	f = Y4_PF_HIT0;
+	if(vx.m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
 	const uint32_t path_flags = sc.no_recursive ? (uint32_t) Y4_BSDF_ALL : (uint32_t) Y4_BSDF_DIFFUSE;
-	if(m.bsdf_flags & path_flags) f |= Y4_PF_PATHS;
-	W.flags[i] = f;
+	if(vx.m.bsdf_flags & path_flags) f |= Y4_PF_PATHS;
+	return true;
 }
 
 // number of samples doLightEstimation takes from light L (integrator_montecarlo.cc:396)
@@ -121,26 +132,26 @@ Y4_HD int y4_light_num_samples(const Y4PtScene &sc, const Y4PtLight &L)
 	return (int) ceilf(xmul((float) L.samples, sc.aa_light_sample_multiplier));
 }
 
-// ---- stage: k-th sample of one light at the current vertex ---------------------------------------
+// does this path take sample k of a light now?  (shared by the sample and the resolve step)
+Y4_HD bool y4_direct_active(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t f, bool all_lights, int light, int k, int &l, int &num_samples)
+{
+	if(!(f & Y4_PF_DIRECT) || (!all_lights && !(f & Y4_PF_ALIVE))) return false;
+	l = all_lights ? light : (int) W.lnum[i];
+	num_samples = y4_light_num_samples(sc, sc.lights[l]);
+	return k < num_samples;
+}
+
+// ---- step: k-th sample of one light at vertex `vx` -------------------------------------------------
 // all_lights: vertex = camera hit (estimateAllDirectLight, light index given);
 // otherwise : vertex = current path vertex, light = W.lnum[i] (estimateOneDirectLight).
-Y4_HD void y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, bool all_lights, int light, int k)
+// Returns the mask of shadow-ray slots written (bit q -> W.sray[q * n + i]).
+Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, bool all_lights, int light, int k, const Y4Vertex &vx)
 {
 	const uint32_t n = W.n;
-	W.sray[i] = y4_null_ray(); W.sray[n + i] = y4_null_ray();
-	st3(W.scontrib, i, c3f(0.f)); st3(W.scontrib, n + i, c3f(0.f));
-	const uint32_t f = W.flags[i];
-	if(!(f & Y4_PF_DIRECT) || (!all_lights && !(f & Y4_PF_ALIVE))) return;
-	const int l = all_lights ? light : (int) W.lnum[i];
+	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1);
+	int l, num_samples;
+	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return 0u;
 	const Y4PtLight &L = sc.lights[l];
-	const int num_samples = y4_light_num_samples(sc, L);
-	if(k >= num_samples) return;
-	const Y4Ray r = all_lights ? y4_primary_ray(sc, W, ps, i) : W.ray[i];
-	const Y4Hit h = all_lights ? W.hit0[i] : W.hit[i];
-	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
-	const Y4Surf sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
-	const Y4PtMaterial m = sc.mats[sp.mat];
-	const V3 wo = xneg(d);
 	float s1 = 0.f, s2 = 0.f;
 	if(L.type != Y4GPU_LIGHT_POINT)
 	{
@@ -150,29 +161,34 @@ Y4_HD void y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 		for(int q = 0; q <= k; ++q) { s1 = y4_halton_next(h2); s2 = y4_halton_next(h3); }
 	}
 	Y4DirectOut out;
-	y4_direct_sample(sc, L, m, sp, wo, s1, s2, out);
-	const bool cast = L.cast_shadows && m.receive_shadows;
+	y4_direct_sample(sc, L, vx.m, vx.sp, vx.wo, s1, s2, out);
+	const bool cast = L.cast_shadows && vx.m.receive_shadows;
+	uint32_t mask = 0u;
 	for(int q = 0; q < 2; ++q)
 	{
-		if(!out.valid[q]) continue;
-		if(cast) W.sray[q * n + i] = out.ray[q];
-		st3(W.scontrib, q * n + i, out.contrib[q]);
+		st3(W.scontrib, q * n + i, out.contrib[q]);           // zero when the sample is invalid
+		if(!out.valid[q] || !cast) continue;
+		W.sray[q * n + i] = out.ray[q];
+		mask |= 1u << q;
 	}
+	if(mask & 1u) f |= Y4_PF_S0;
+	if(mask & 2u) f |= Y4_PF_S1;
+	return mask;
 }
 
-// ---- stage: fold the shadow-ray results of sample k into the light's estimators ------------------
-Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, bool all_lights, int light, int k)
+// ---- step: fold the shadow-ray results of sample k into the light's estimators ---------------------
+Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t &f, bool all_lights, int light, int k)
 {
 	const uint32_t n = W.n;
-	const uint32_t f = W.flags[i];
-	if(!(f & Y4_PF_DIRECT) || (!all_lights && !(f & Y4_PF_ALIVE))) return;
-	const int l = all_lights ? light : (int) W.lnum[i];
+	int l, num_samples;
+	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return;
 	const Y4PtLight &L = sc.lights[l];
-	const int num_samples = y4_light_num_samples(sc, L);
-	if(k >= num_samples) return;
-	C3 a = ld3(W.acc_a, i), b = ld3(W.acc_b, i);
-	if(W.shit[i].prim < 0) a = cadd(a, ld3(W.scontrib, i));
-	if(W.shit[n + i].prim < 0) b = cadd(b, ld3(W.scontrib, n + i));
+	// running sums over the light's samples live in acc_a/acc_b only between samples (k > 0)
+	C3 a = c3f(0.f), b = c3f(0.f);
+	if(k > 0) { a = ld3(W.acc_a, i); b = ld3(W.acc_b, i); }
+	if(!(f & Y4_PF_S0) || W.shit[i].prim < 0) a = cadd(a, ld3(W.scontrib, i));
+	if(!(f & Y4_PF_S1) || W.shit[n + i].prim < 0) b = cadd(b, ld3(W.scontrib, n + i));
+	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1);
 	if(k < num_samples - 1) { st3(W.acc_a, i, a); st3(W.acc_b, i, b); return; }
 	// last sample of this light: doLightEstimation's result
 	C3 dl = c3f(0.f);
@@ -183,7 +199,6 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 		dl = cadd(dl, cscale(a, inv));
 		dl = cadd(dl, cscale(b, inv));
 	}
-	st3(W.acc_a, i, c3f(0.f)); st3(W.acc_b, i, c3f(0.f));
 	if(all_lights) st3(W.col, i, cadd(ld3(W.col, i), dl));                     // estimateAllDirectLight: col += ...
 	else
 	{
@@ -191,30 +206,25 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 		C3 lcol = cscale(dl, (float) sc.n_lights);
 		lcol = cadd(lcol, ld3(W.lcol, i));
 		st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, ld3(W.thr, i))));
-		st3(W.lcol, i, c3f(0.f));
-		W.flags[i] = f & ~(uint32_t) Y4_PF_DIRECT;
+		f &= ~(uint32_t) Y4_PF_DIRECT;
 	}
 }
 
-// ---- stage: BSDF sample that extends sub-path `sub` at bounce `depth` (integrate(), :163-231) ------
-Y4_HD void y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub)
+// ---- step: BSDF sample that extends sub-path `sub` at bounce `depth` (integrate(), :163-231) --------
+// returns true when W.ray[i] holds the next ray of the path
+Y4_HD bool y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, int depth, int sub)
 {
-	uint32_t f = W.flags[i];
 	if(depth == 0)
 	{
 		f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIFF1 | Y4_PF_DIRECT);
-		W.flags[i] = f;
-		if(!(f & Y4_PF_PATHS)) { W.ray[i] = y4_null_ray(); return; }
+		if(!(f & Y4_PF_PATHS)) return false;
 	}
-	else if(!(f & Y4_PF_ALIVE)) { W.ray[i] = y4_null_ray(); return; }
+	else if(!(f & Y4_PF_ALIVE)) return false;
 	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
 	const uint32_t offs = (uint32_t) sc.n_paths * s.sample + s.offset + (uint32_t) sub;
 	const Y4Ray r = depth == 0 ? y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy)) : W.ray[i];
 	const Y4Hit h = depth == 0 ? W.hit0[i] : W.hit[i];
-	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
-	const Y4Surf sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
-	const Y4PtMaterial m = sc.mats[sp.mat];
-	const V3 pwo = xneg(d);
+	const Y4Vertex vx = y4_vertex(sc, r, h);
 	float s1, s2; uint32_t sflags;
 	if(depth == 0)
 	{
@@ -230,37 +240,35 @@ Y4_HD void y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4P
 	}
 	V3 wi = v3(0.f, 0.f, 1.f);
 	float w = 0.f, pdf; bool sampled;
-	C3 scol = y4_mat_sample(m, sp, pwo, s1, s2, sflags, wi, w, pdf, sampled);
+	C3 scol = y4_mat_sample(vx.m, vx.sp, vx.wo, s1, s2, sflags, wi, w, pdf, sampled);
 	scol = cscale(scol, w);
 	if(depth == 0) st3(W.thr, i, scol);
 	else
 	{
-		if(cblack(scol)) { W.flags[i] = f & ~(uint32_t) Y4_PF_ALIVE; W.ray[i] = y4_null_ray(); return; }
+		if(cblack(scol)) { f &= ~(uint32_t) Y4_PF_ALIVE; return false; }
 		st3(W.thr, i, cmul(ld3(W.thr, i), scol));
 	}
-	if(!sampled) { W.flags[i] = f & ~(uint32_t) Y4_PF_ALIVE; W.ray[i] = y4_null_ray(); return; }   // reference: direction undefined
-	W.ray[i] = y4_mk_ray(sp.p, sc.ray_min_dist, wi, -1.f);
-	W.flags[i] = f | Y4_PF_ALIVE;
+	if(!sampled) { f &= ~(uint32_t) Y4_PF_ALIVE; return false; }   // reference: direction undefined
+	W.ray[i] = y4_mk_ray(vx.sp.p, sc.ray_min_dist, wi, -1.f);
+	f |= Y4_PF_ALIVE;
+	return true;
 }
 
-// ---- stage: the extended ray's hit (integrate(), :191-207 and :232-266) ----------------------------
-Y4_HD void y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub)
+// ---- step: the extended ray's hit (integrate(), :191-207 and :232-266) ------------------------------
+// returns true (and fills vx) when the vertex wants a one-light estimate (Y4_PF_DIRECT set, W.lnum chosen)
+Y4_HD bool y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, int depth, int sub, Y4Vertex &vx)
 {
-	uint32_t f = W.flags[i];
-	if(!(f & Y4_PF_ALIVE)) return;
+	if(!(f & Y4_PF_ALIVE)) return false;
 	const Y4Hit h = W.hit[i];
-	if(h.prim < 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return; }     // hit background: continue / break
-	const Y4Ray r = W.ray[i];
-	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
-	const Y4Surf sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
-	const Y4PtMaterial m = sc.mats[sp.mat];
-	const V3 pwo = xneg(d);
+	if(h.prim < 0) { f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return false; }     // hit background: continue / break
+	vx = y4_vertex(sc, W.ray[i], h);
+	const Y4PtMaterial &m = vx.m;
 	C3 emit = c3f(0.f);
 	bool direct;
 	if(depth == 0)
 	{
 		if(m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIFF1; else f &= ~(uint32_t) Y4_PF_DIFF1;
-		if(m.bsdf_flags & Y4_BSDF_EMIT) emit = y4_mat_emit(m, sp, pwo);
+		if(m.bsdf_flags & Y4_BSDF_EMIT) emit = y4_mat_emit(m, vx.sp, vx.wo);
 		direct = m.is_diffuse != 0;     // a non-diffuse vertex evaluates to exactly 0 for every light sample
 	}
 	else
@@ -273,7 +281,7 @@ Y4_HD void y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 			const float random_value = y4_hash_uniform(sc.rr_seed ^ s.offset, s.sample, (uint32_t) (sub * 64 + depth));
 			C3 thr = ld3(W.thr, i);
 			const float probability = cmax(thr);
-			if(probability <= 0.f || probability < random_value) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return; }
+			if(probability <= 0.f || probability < random_value) { f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return false; }
 			st3(W.thr, i, cscale(thr, xdiv(1.f, probability)));
 		}
 	}
@@ -288,15 +296,83 @@ Y4_HD void y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 		const int lnum = (int) xmul(y4_halton_next(h2), (float) sc.n_lights);
 		W.lnum[i] = (uint32_t) (lnum < sc.n_lights - 1 ? lnum : sc.n_lights - 1);
 		st3(W.lcol, i, emit);
-		W.flags[i] = f | Y4_PF_DIRECT;
+		f |= Y4_PF_DIRECT;
+		return true;
 	}
-	else
+	// lcol = 0 (* num_lights) + emit;  path_col += lcol * throughput
+	const C3 lcol = cadd(c3f(0.f), emit);
+	st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, ld3(W.thr, i))));
+	f &= ~(uint32_t) Y4_PF_DIRECT;
+	return false;
+}
+
+// ==== fused wavefront stages ===========================================================================
+// Each returns a push mask: bit 0/1 = shadow-ray slot 0/1 written, bit 2 = the path goes on the stage's
+// output path queue.  y4_pt.cu runs them as kernels over compacted index queues; tests/emu as loops.
+enum : uint32_t { Y4_PUSH_S0 = 1u, Y4_PUSH_S1 = 2u, Y4_PUSH_PATH = 4u };
+
+// camera-ray hit + first direct-light sample (light l0, k = 0; l0 < 0: scene without lights).
+// Output queue: paths that hit a surface and have more to do (more light samples or sub-paths).
+Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l0)
+{
+	uint32_t f; Y4Vertex vx;
+	uint32_t push = 0u;
+	if(y4_pt_primary(sc, W, i, f, vx))
 	{
-		// lcol = 0 (* num_lights) + emit;  path_col += lcol * throughput
-		const C3 lcol = cadd(c3f(0.f), emit);
-		st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, ld3(W.thr, i))));
-		W.flags[i] = f & ~(uint32_t) Y4_PF_DIRECT;
+		if(l0 >= 0) push |= y4_pt_direct(sc, W, ps, i, f, true, l0, 0, vx);
+		if(f & (Y4_PF_DIRECT | Y4_PF_PATHS)) push |= Y4_PUSH_PATH;
 	}
+	W.flags[i] = f;
+	return push;
+}
+
+// resolve sample (l_prev, k_prev), take sample (l, k); camera-hit vertex (all_lights) or current path vertex
+Y4_HD uint32_t y4_stage_direct_step(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, bool all_lights, int l_prev, int k_prev, int l, int k)
+{
+	uint32_t f = W.flags[i];
+	y4_pt_direct_resolve(sc, W, i, f, all_lights, l_prev, k_prev);
+	uint32_t push = 0u;
+	int ll, ns;
+	if(y4_direct_active(sc, W, i, f, all_lights, l, k, ll, ns))
+	{
+		const Y4Ray r = all_lights ? y4_primary_ray(sc, W, ps, i) : W.ray[i];
+		const Y4Vertex vx = y4_vertex(sc, r, all_lights ? W.hit0[i] : W.hit[i]);
+		push = y4_pt_direct(sc, W, ps, i, f, all_lights, l, k, vx);
+	}
+	W.flags[i] = f;
+	return push;
+}
+
+// start sub-path `sub` at the camera hit: [resolve the last all-lights sample] + BSDF sample at depth 0
+Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l_last, int k_last, int sub)
+{
+	uint32_t f = W.flags[i];
+	if(l_last >= 0) y4_pt_direct_resolve(sc, W, i, f, true, l_last, k_last);
+	const bool go = y4_pt_bounce_sample(sc, W, ps, i, f, 0, sub);
+	W.flags[i] = f;
+	return go ? (uint32_t) Y4_PUSH_PATH : 0u;
+}
+
+// path vertex: hit processing (emission, Russian roulette, light choice) + first sample of the chosen light.
+Y4_HD uint32_t y4_stage_vertex(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub)
+{
+	uint32_t f = W.flags[i];
+	Y4Vertex vx;
+	uint32_t push = 0u;
+	if(y4_pt_bounce_hit(sc, W, ps, i, f, depth, sub, vx)) push = y4_pt_direct(sc, W, ps, i, f, false, -1, 0, vx);
+	W.flags[i] = f;
+	return push;
+}
+
+// close the vertex: [resolve the last light sample] + BSDF sample for the next bounce
+Y4_HD uint32_t y4_stage_extend(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub, int k_last)
+{
+	uint32_t f = W.flags[i];
+	if(k_last >= 0) y4_pt_direct_resolve(sc, W, i, f, false, -1, k_last);
+	bool go = false;
+	if(depth + 1 < sc.bounces) go = y4_pt_bounce_sample(sc, W, ps, i, f, depth + 1, sub);
+	W.flags[i] = f;
+	return go ? (uint32_t) Y4_PUSH_PATH : 0u;
 }
 
 // ---- stage: close the pixel-sample and splat it into the film ----------------------------------------

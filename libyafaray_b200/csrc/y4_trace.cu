@@ -20,11 +20,15 @@ constexpr int kTraceThreads = 256;
 //    traversal stack so the warp returns to (convergent) node traversal;
 //  * shadow rays leave at the first accepted blocker (any-hit) and their lane is refilled.
 // Results do not depend on the schedule: closest hits use the order-independent rule y4_accept_t.
-template<int KIND, bool COUNT, int MINB>
+// QUEUE: the batch is an index queue built on the device (the path tracer's compacted wavefronts):
+// entry q names ray/hit slot queue[q] and the entry count is read from *queue_count.
+template<int KIND, bool COUNT, int MINB, bool QUEUE>
 __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const Y4Ray *__restrict__ rays, uint64_t n, Y4Hit *__restrict__ out,
                                                          unsigned long long *__restrict__ work_counter, unsigned long long *__restrict__ visit,
-                                                         int fetch_threshold, int postpone_div)
+                                                         int fetch_threshold, int postpone_div,
+                                                         const uint32_t *__restrict__ queue, const uint32_t *__restrict__ queue_count)
 {
+	if(QUEUE) n = __ldg(queue_count);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t lt_mask = (1u << lane) - 1u;
 	const uint32_t vis_bit = KIND == Y4_TRACE_CLOSEST ? Y4_TRI_VIS_CLOSEST : Y4_TRI_VIS_SHADOW;
@@ -52,14 +56,15 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 			const uint64_t mine = base + __popc(idle & lt_mask);
 			if(!have && mine < n)
 			{
-				const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + mine));
-				const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + mine) + 1);
+				const uint64_t slot_i = QUEUE ? (uint64_t) __ldg(queue + mine) : mine;
+				const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + slot_i));
+				const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + slot_i) + 1);
 				Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
 				const Y4PreparedRay pr = y4_prepare_ray(r, KIND);
 				rc = y4_ray_ctx(pr.o, pr.d);
 				t_lo = pr.t_lo; t_hi = pr.t_hi;
 				hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
-				ray_i = mine; sp = 0; have = true;
+				ray_i = slot_i; sp = 0; have = true;
 				// virtual parent of the root: child_base 0, imask = slot 0, hit bit at slot 0's priority
 				// empty scene or empty interval (the path tracer parks finished paths as null rays): nothing to visit
 				ngroup.x = 0u; ngroup.y = (bvh.n_tris && pr.t_hi > pr.t_lo) ? ((1u << (24u + rc.oct_inv)) | 1u) : 0u;
@@ -181,24 +186,35 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, con
 	}
 }
 
-template<int KIND, bool COUNT, int MINB>
-int launch_k(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out)
+struct TraceArgs
 {
-	int per_sm = 0;
-	Y4_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<KIND, COUNT, MINB>, kTraceThreads, 0));
-	if(per_sm < 1) per_sm = 1;
-	const uint64_t want = (n + kTraceThreads - 1) / kTraceThreads;
+	const Y4Ray *rays; uint64_t n; Y4Hit *out;
+	unsigned long long *work_counter, *visit;
+	const uint32_t *queue, *queue_count;
+};
+
+template<int KIND, bool COUNT, int MINB, bool QUEUE>
+int launch_k(y4gpu_ctx *ctx, const TraceArgs &a)
+{
+	static int per_sm_cached[16] = {0};          // per device
+	int &per_sm = per_sm_cached[ctx->device & 15];
+	if(per_sm < 1)
+	{
+		Y4_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace<KIND, COUNT, MINB, QUEUE>, kTraceThreads, 0));
+		if(per_sm < 1) per_sm = 1;
+	}
+	const uint64_t want = (a.n + kTraceThreads - 1) / kTraceThreads;
 	const uint64_t full = (uint64_t) ctx->sm_count * per_sm;     // persistent: one wave of resident CTAs
 	const int grid = (int) (want < full ? want : full);
-	k_trace<KIND, COUNT, MINB><<<grid, kTraceThreads, 0, ctx->stream>>>(ctx->view(), d_rays, n, d_out, reinterpret_cast<unsigned long long *>(ctx->d_work_counter),
-	                                                                   ctx->d_visit_counters, ctx->fetch_threshold, ctx->postpone_div);
+	k_trace<KIND, COUNT, MINB, QUEUE><<<grid, kTraceThreads, 0, ctx->stream>>>(ctx->view(), a.rays, a.n, a.out, a.work_counter, a.visit,
+	                                                                          ctx->fetch_threshold, ctx->postpone_div, a.queue, a.queue_count);
 	return Y4GPU_OK;
 }
-template<int KIND, bool COUNT>
-int launch(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out)
+template<int KIND, bool QUEUE>
+int launch(y4gpu_ctx *ctx, bool counted, const TraceArgs &a)
 {
-	if(COUNT) return launch_k<KIND, true, 3>(ctx, d_rays, n, d_out);
-	return ctx->min_blocks >= 4 ? launch_k<KIND, false, 4>(ctx, d_rays, n, d_out) : launch_k<KIND, false, 3>(ctx, d_rays, n, d_out);
+	if(counted) return launch_k<KIND, true, 3, QUEUE>(ctx, a);
+	return ctx->min_blocks >= 4 ? launch_k<KIND, false, 4, QUEUE>(ctx, a) : launch_k<KIND, false, 3, QUEUE>(ctx, a);
 }
 
 } // namespace
@@ -210,15 +226,34 @@ int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays,
 	Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_work_counter, 0, sizeof(unsigned long long), st));
 	if(counted) Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_visit_counters, 0, 3 * sizeof(unsigned long long), st));
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+	TraceArgs a; a.rays = d_rays; a.n = n; a.out = d_out; a.work_counter = reinterpret_cast<unsigned long long *>(ctx->d_work_counter);
+	a.visit = ctx->d_visit_counters; a.queue = nullptr; a.queue_count = nullptr;
 	int rc;
-	if(kind == Y4_TRACE_CLOSEST) rc = counted ? launch<Y4_TRACE_CLOSEST, true>(ctx, d_rays, n, d_out) : launch<Y4_TRACE_CLOSEST, false>(ctx, d_rays, n, d_out);
-	else if(kind == Y4_TRACE_SHADOW) rc = counted ? launch<Y4_TRACE_SHADOW, true>(ctx, d_rays, n, d_out) : launch<Y4_TRACE_SHADOW, false>(ctx, d_rays, n, d_out);
+	if(kind == Y4_TRACE_CLOSEST) rc = launch<Y4_TRACE_CLOSEST, false>(ctx, counted, a);
+	else if(kind == Y4_TRACE_SHADOW) rc = launch<Y4_TRACE_SHADOW, false>(ctx, counted, a);
 	else { ctx->err = "bad trace kind"; return Y4GPU_ERR_ARG; }
 	if(rc) return rc;
 	Y4_CUDA(ctx, cudaGetLastError());
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
 	ctx->stats.kernel_launches++;
 	ctx->stats.last_trace_rays = n;
+	return Y4GPU_OK;
+}
+
+// Wavefront entry of the path tracer: the batch is either dense (queue == null, n rays) or a device-built
+// index queue of at most n_max entries whose length is *queue_count.  work_counter must be zero (the
+// caller hands out a fresh pre-zeroed slot per launch); visit (3 counters) is accumulated when counted.
+int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays, Y4Hit *d_out, uint64_t n_max,
+                         const uint32_t *d_queue, const uint32_t *d_queue_count, unsigned long long *d_work_counter, unsigned long long *d_visit)
+{
+	if(n_max == 0) return Y4GPU_OK;
+	TraceArgs a; a.rays = d_rays; a.n = n_max; a.out = d_out; a.work_counter = d_work_counter; a.visit = d_visit; a.queue = d_queue; a.queue_count = d_queue_count;
+	int rc;
+	if(kind == Y4_TRACE_CLOSEST) rc = d_queue ? launch<Y4_TRACE_CLOSEST, true>(ctx, counted, a) : launch<Y4_TRACE_CLOSEST, false>(ctx, counted, a);
+	else if(kind == Y4_TRACE_SHADOW) rc = d_queue ? launch<Y4_TRACE_SHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_SHADOW, false>(ctx, counted, a);
+	else { ctx->err = "bad trace kind"; return Y4GPU_ERR_ARG; }
+	if(rc) return rc;
+	ctx->stats.kernel_launches++;
 	return Y4GPU_OK;
 }
 

@@ -16,10 +16,12 @@ struct EmuBvh
 };
 void emu_build(const float *verts, const uint32_t *flags, int n, int leaf_max, EmuBvh &out);
 
-static void trace(const Y4Bvh8 &bvh, int kind, const Y4Ray *rays, size_t n, Y4Hit *hits)
+// queue == null: dense batch of n rays; else n index entries
+static void trace(const Y4Bvh8 &bvh, int kind, const Y4Ray *rays, const uint32_t *queue, size_t n, Y4Hit *hits)
 {
-	for(size_t i = 0; i < n; ++i)
+	for(size_t q = 0; q < n; ++q)
 	{
+		const size_t i = queue ? queue[q] : q;
 		const Y4PreparedRay pr = y4_prepare_ray(rays[i], kind);
 		uint2 stack[Y4_STACK_SIZE];
 		hits[i].t = 0.f; hits[i].bu = 0.f; hits[i].bv = 0.f; hits[i].prim = -1;
@@ -27,6 +29,14 @@ static void trace(const Y4Bvh8 &bvh, int kind, const Y4Ray *rays, size_t n, Y4Hi
 		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray<Y4_TRACE_CLOSEST>(bvh, pr, hits[i], stack, nullptr, nullptr, nullptr, nullptr, 0);
 		else y4_trace_ray<Y4_TRACE_SHADOW>(bvh, pr, hits[i], stack, nullptr, nullptr, nullptr, nullptr, 0);
 	}
+}
+
+// what k_pt_stage's queue appends do
+static void push(uint32_t mask, uint32_t i, uint32_t n, std::vector<uint32_t> *path_q, std::vector<uint32_t> *shadow_q)
+{
+	if(shadow_q && (mask & Y4_PUSH_S0)) shadow_q->push_back(i);
+	if(shadow_q && (mask & Y4_PUSH_S1)) shadow_q->push_back(n + i);
+	if(path_q && (mask & Y4_PUSH_PATH)) path_q->push_back(i);
 }
 
 extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material *mats, uint32_t n_mat, const y4gpu_pt_light *lights, uint32_t n_light,
@@ -72,30 +82,46 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	W.ray = ray.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = scontrib.data();
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
 	for(uint32_t i = 0; i < n; ++i) { pix[i] = i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
+	// same stage sequence as y4gpu_pt_render_pass (y4_pt.cu), queues as vectors
 	for(uint32_t i = 0; i < n; ++i) y4_pt_gen(sc, W, ps, i);
-	trace(bvh, Y4_TRACE_CLOSEST, W.ray, n, W.hit);
-	for(uint32_t i = 0; i < n; ++i) y4_pt_primary(sc, W, i);
+	trace(bvh, Y4_TRACE_CLOSEST, W.ray, nullptr, n, W.hit);
+	std::vector<std::pair<int, int>> all_lk;
 	for(int l = 0; l < sc.n_lights; ++l)
-		for(int k = 0; k < y4_light_num_samples(sc, sc.lights[l]); ++k)
-		{
-			for(uint32_t i = 0; i < n; ++i) y4_pt_direct(sc, W, ps, i, true, l, k);
-			trace(bvh, Y4_TRACE_SHADOW, W.sray, 2ull * n, W.shit);
-			for(uint32_t i = 0; i < n; ++i) y4_pt_direct_resolve(sc, W, i, true, l, k);
-		}
+		for(int k = 0; k < y4_light_num_samples(sc, sc.lights[l]); ++k) all_lk.push_back(std::make_pair(l, k));
+	std::vector<uint32_t> q_hit0, q_shadow, q_cur, q_next;
+	for(uint32_t i = 0; i < n; ++i) push(y4_stage_primary(sc, W, ps, i, all_lk.empty() ? -1 : all_lk[0].first), i, n, &q_hit0, &q_shadow);
+	for(size_t j = 0; j < all_lk.size(); ++j)
+	{
+		trace(bvh, Y4_TRACE_SHADOW, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
+		if(j + 1 == all_lk.size()) break;
+		q_shadow.clear();
+		for(uint32_t i : q_hit0) push(y4_stage_direct_step(sc, W, ps, i, true, all_lk[j].first, all_lk[j].second, all_lk[j + 1].first, all_lk[j + 1].second), i, n, nullptr, &q_shadow);
+	}
 	for(int sub = 0; sub < sc.n_paths; ++sub)
+	{
+		q_cur.clear();
+		const bool res = sub == 0 && !all_lk.empty();
+		for(uint32_t i : q_hit0) push(y4_stage_start(sc, W, ps, i, res ? all_lk.back().first : -1, res ? all_lk.back().second : -1, sub), i, n, &q_cur, nullptr);
 		for(int depth = 0; depth < sc.bounces; ++depth)
 		{
-			for(uint32_t i = 0; i < n; ++i) y4_pt_bounce_sample(sc, W, ps, i, depth, sub);
-			trace(bvh, Y4_TRACE_CLOSEST, W.ray, n, W.hit);
-			for(uint32_t i = 0; i < n; ++i) y4_pt_bounce_hit(sc, W, ps, i, depth, sub);
-			if(sc.n_lights == 0) continue;
-			for(int k = 0; k < max_ls; ++k)
+			trace(bvh, Y4_TRACE_CLOSEST, W.ray, q_cur.data(), q_cur.size(), W.hit);
+			q_shadow.clear();
+			for(uint32_t i : q_cur) push(y4_stage_vertex(sc, W, ps, i, depth, sub), i, n, nullptr, &q_shadow);
+			if(sc.n_lights)
 			{
-				for(uint32_t i = 0; i < n; ++i) y4_pt_direct(sc, W, ps, i, false, -1, k);
-				trace(bvh, Y4_TRACE_SHADOW, W.sray, 2ull * n, W.shit);
-				for(uint32_t i = 0; i < n; ++i) y4_pt_direct_resolve(sc, W, i, false, -1, k);
+				trace(bvh, Y4_TRACE_SHADOW, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
+				for(int k = 1; k < max_ls; ++k)
+				{
+					q_shadow.clear();
+					for(uint32_t i : q_cur) push(y4_stage_direct_step(sc, W, ps, i, false, -1, k - 1, -1, k), i, n, nullptr, &q_shadow);
+					trace(bvh, Y4_TRACE_SHADOW, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
+				}
 			}
+			q_next.clear();
+			for(uint32_t i : q_cur) push(y4_stage_extend(sc, W, ps, i, depth, sub, sc.n_lights ? max_ls - 1 : -1), i, n, &q_next, nullptr);
+			q_cur.swap(q_next);
 		}
+	}
 	for(uint32_t i = 0; i < n; ++i) y4_pt_finish_splat(sc, W, ps, i, film_w, film_rgba);
 	return 0;
 }
