@@ -45,6 +45,7 @@ Y4_HD double xdsub(double a, double b) { return a - b; }
 
 #if !defined(__CUDACC__)
 struct uint2 { uint32_t x, y; };
+struct alignas(16) float4 { float x, y, z, w; };
 #endif
 
 struct V3 { float x, y, z; };

@@ -14,6 +14,8 @@
 struct Y4FaureHost
 {
 	std::vector<uint8_t> sigma;
+	std::vector<double> sigma_d;            // the same permutation values as doubles (saves the int->fp64 conversion per digit)
+	unsigned long long magic[50];           // floor(2^64 / prime) + 1: n / prime == mulhi64(n, magic) for every 32-bit n
 	uint16_t offset[50];
 	uint16_t prime[50];
 	double inv_prime[50];
@@ -59,7 +61,8 @@ inline Y4FaureHost y4_faure_build()
 			t.offset[dim] = (uint16_t) t.sigma.size();
 			// the reference's table list reuses the identity base-3 table for dimensions 0, 1, 2 (halton.cc:398-399)
 			const std::vector<int> perm = dim < 3 ? std::vector<int>{0, 1, 2} : y4_faure_perm(p);
-			for(int v : perm) t.sigma.push_back((uint8_t) v);
+			for(int v : perm) { t.sigma.push_back((uint8_t) v); t.sigma_d.push_back((double) v); }
+			t.magic[dim] = p > 1 ? (unsigned long long) ((((unsigned __int128) 1) << 64) / (unsigned) p) + 1ull : 0ull;
 			++dim;
 		}
 		++p;

@@ -8,11 +8,13 @@
 
 struct Y4Pt
 {
-	Y4PtScene h_scene;                 // host copy (device pointers inside)
-	Y4PtScene *d_scene = nullptr;
+	Y4PtScene h_scene;                 // passed to every kernel by value (device pointers inside)
+	std::vector<Y4PtLight> h_lights;   // host copy of the derived lights
+	Y4PtLight *d_lights = nullptr;
 	Y4PtMaterial *d_mats = nullptr;
+	float4 *d_tri_shade = nullptr;
 	float *d_normals = nullptr;
-	uint8_t *d_sigma = nullptr; uint16_t *d_offset = nullptr, *d_prime = nullptr; double *d_inv_prime = nullptr;
+	uint8_t *d_sigma = nullptr; uint16_t *d_offset = nullptr, *d_prime = nullptr; double *d_inv_prime = nullptr, *d_sigma_d = nullptr; unsigned long long *d_magic = nullptr;
 	bool scene_set = false;
 	y4gpu_pt_params params = {};
 	int max_light_samples = 1;
@@ -54,7 +56,7 @@ struct StageQueues
 	uint32_t *sh_q, *sh_count;           // shadow rays to trace: slot index into W.sray / W.shit
 };
 
-__global__ void __launch_bounds__(kPtThreads) k_pt_gen(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, const uint32_t *__restrict__ pixel_list,
+__global__ void __launch_bounds__(kPtThreads) k_pt_gen(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, const uint32_t *__restrict__ pixel_list,
                                                         uint64_t first, uint32_t ns_local, int shard_index, int shard_count)
 {
 	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x)
@@ -63,12 +65,12 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_gen(const Y4PtScene *__restri
 		const uint64_t slot = g / ns_local;
 		W.pix[i] = pixel_list ? pixel_list[slot] : (uint32_t) slot;
 		W.samp[i] = (uint32_t) shard_index + (uint32_t) (g % ns_local) * (uint32_t) shard_count;
-		y4_pt_gen(*sc, W, ps, i);
+		y4_pt_gen(sc, W, ps, i);
 	}
 }
 
 template<int STAGE>
-__global__ void __launch_bounds__(kPtThreads) k_pt_stage(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, StageArgs a, StageQueues Q)
+__global__ void __launch_bounds__(kPtThreads) k_pt_stage(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, StageArgs a, StageQueues Q)
 {
 	const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
 	const uint32_t count = Q.in_q ? *Q.in_count : W.n;
@@ -80,11 +82,11 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_stage(const Y4PtScene *__rest
 		if(q < count)
 		{
 			i = Q.in_q ? Q.in_q[q] : q;
-			if(STAGE == kStPrimary) push = y4_stage_primary(*sc, W, ps, i, a.l);
-			else if(STAGE == kStDirectStep) push = y4_stage_direct_step(*sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
-			else if(STAGE == kStStart) push = y4_stage_start(*sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
-			else if(STAGE == kStVertex) push = y4_stage_vertex(*sc, W, ps, i, a.depth, a.sub);
-			else push = y4_stage_extend(*sc, W, ps, i, a.depth, a.sub, a.k_prev);
+			if(STAGE == kStPrimary) push = y4_stage_primary(sc, W, ps, i, a.l);
+			else if(STAGE == kStDirectStep) push = y4_stage_direct_step(sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
+			else if(STAGE == kStStart) push = y4_stage_start(sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
+			else if(STAGE == kStVertex) push = y4_stage_vertex(sc, W, ps, i, a.depth, a.sub);
+			else push = y4_stage_extend(sc, W, ps, i, a.depth, a.sub, a.k_prev);
 		}
 		if(STAGE == kStPrimary || STAGE == kStDirectStep || STAGE == kStVertex)
 		{
@@ -112,9 +114,14 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_stage(const Y4PtScene *__rest
 	}
 }
 
-__global__ void __launch_bounds__(kPtThreads) k_pt_splat(const Y4PtScene *__restrict__ sc, Y4PtWave W, Y4PtPass ps, float *film_w, float *film_rgba)
+__global__ void __launch_bounds__(kPtThreads) k_pt_tri_shade(const float *__restrict__ verts, const uint32_t *__restrict__ tri_flags, uint32_t n_mats, uint64_t n_tri, float4 *__restrict__ out)
 {
-	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_finish_splat(*sc, W, ps, i, film_w, film_rgba);
+	for(uint64_t t = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x; t < n_tri; t += (uint64_t) gridDim.x * blockDim.x) out[t] = y4_tri_shade(verts, tri_flags, n_mats, t);
+}
+
+__global__ void __launch_bounds__(kPtThreads) k_pt_splat(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, float *film_w, float *film_rgba)
+{
+	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_finish_splat(sc, W, ps, i, film_w, film_rgba);
 }
 
 inline int pt_grid(const y4gpu_ctx *ctx, uint32_t n)
@@ -135,13 +142,13 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt *pt, uint32_t cap)
 	pt_free_wave(pt);
 	const size_t n = cap;
 	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 32 + 16 + 16 /*ray hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/
-	                          + 5 * 4 /*queues*/) + 512;
+	                          + 16 /*lsamp*/ + 5 * 4 /*queues*/) + 512;
 	Y4_CUDA(ctx, cudaMalloc(&pt->wave_mem, bytes));
 	char *p = (char *) pt->wave_mem;
 	auto take = [&](size_t b) { char *r = p; p += (b + 15) & ~(size_t) 15; return (void *) r; };
 	Y4PtWave &W = pt->wave;
 	W.col = (float *) take(n * 16); W.pcol = (float *) take(n * 16); W.thr = (float *) take(n * 16); W.lcol = (float *) take(n * 16);
-	W.acc_a = (float *) take(n * 16); W.acc_b = (float *) take(n * 16);
+	W.acc_a = (float *) take(n * 16); W.acc_b = (float *) take(n * 16); W.lsamp = (float *) take(n * 16);
 	W.ray = (Y4Ray *) take(n * 32); W.hit = (Y4Hit *) take(n * 16); W.hit0 = (Y4Hit *) take(n * 16);
 	W.sray = (Y4Ray *) take(2 * n * 32); W.shit = (Y4Hit *) take(2 * n * 16); W.scontrib = (float *) take(2 * n * 16);
 	W.pix = (uint32_t *) take(n * 4); W.samp = (uint32_t *) take(n * 4); W.flags = (uint32_t *) take(n * 4); W.lnum = (uint32_t *) take(n * 4);
@@ -166,8 +173,8 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	Y4Pt *pt = ctx->pt;
 	if(!pt) return;
 	pt_free_wave(pt);
-	cudaFree(pt->d_scene); cudaFree(pt->d_mats); cudaFree(pt->d_normals);
-	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime);
+	cudaFree(pt->d_lights); cudaFree(pt->d_mats); cudaFree(pt->d_normals); cudaFree(pt->d_tri_shade);
+	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime); cudaFree(pt->d_sigma_d); cudaFree(pt->d_magic);
 	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); cudaFree(pt->d_pixel_list);
 	cudaFree(pt->d_counters); cudaFreeHost(pt->h_counters);
 	if(pt->ev0) cudaEventDestroy(pt->ev0);
@@ -214,11 +221,18 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	derive_film(*params, sc);
 	sc.n_lights = (int) n_light; sc.n_mats = (int) n_mat;
 	pt->max_light_samples = 1;
+	pt->h_lights.resize(n_light);
 	for(uint32_t i = 0; i < n_light; ++i)
 	{
-		sc.lights[i] = derive_light(lights[i]);
-		const int ns = y4_light_num_samples(sc, sc.lights[i]);
+		pt->h_lights[i] = derive_light(lights[i]);
+		const int ns = y4_light_num_samples(sc, pt->h_lights[i]);
 		if(ns > pt->max_light_samples) pt->max_light_samples = ns;
+	}
+	cudaFree(pt->d_lights); pt->d_lights = nullptr;
+	if(n_light)
+	{
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_lights, n_light * sizeof(Y4PtLight)));
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_lights, pt->h_lights.data(), n_light * sizeof(Y4PtLight), cudaMemcpyHostToDevice, st));
 	}
 	std::vector<Y4PtMaterial> hm(n_mat);
 	for(uint32_t i = 0; i < n_mat; ++i) hm[i] = derive_material(mats[i]);
@@ -240,11 +254,20 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		Y4_CUDA(ctx, cudaMemcpy(pt->d_offset, fh.offset, sizeof(fh.offset), cudaMemcpyHostToDevice));
 		Y4_CUDA(ctx, cudaMemcpy(pt->d_prime, fh.prime, sizeof(fh.prime), cudaMemcpyHostToDevice));
 		Y4_CUDA(ctx, cudaMemcpy(pt->d_inv_prime, fh.inv_prime, sizeof(fh.inv_prime), cudaMemcpyHostToDevice));
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_sigma_d, fh.sigma_d.size() * sizeof(double))); Y4_CUDA(ctx, cudaMalloc(&pt->d_magic, sizeof(fh.magic)));
+		Y4_CUDA(ctx, cudaMemcpy(pt->d_sigma_d, fh.sigma_d.data(), fh.sigma_d.size() * sizeof(double), cudaMemcpyHostToDevice));
+		Y4_CUDA(ctx, cudaMemcpy(pt->d_magic, fh.magic, sizeof(fh.magic), cudaMemcpyHostToDevice));
 	}
-	sc.mats = pt->d_mats; sc.verts = ctx->d_verts; sc.tri_flags = ctx->d_flags; sc.normals = pt->d_normals;
-	sc.lds.sigma = pt->d_sigma; sc.lds.offset = pt->d_offset; sc.lds.prime = pt->d_prime; sc.lds.inv_prime = pt->d_inv_prime;
-	if(!pt->d_scene) Y4_CUDA(ctx, cudaMalloc(&pt->d_scene, sizeof(Y4PtScene)));
-	Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_scene, &sc, sizeof(Y4PtScene), cudaMemcpyHostToDevice, st));
+	cudaFree(pt->d_tri_shade); pt->d_tri_shade = nullptr;
+	if(ctx->n_tri)
+	{
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_tri_shade, ctx->n_tri * sizeof(float4)));
+		const uint64_t want = (ctx->n_tri + kPtThreads - 1) / kPtThreads, full = (uint64_t) ctx->sm_count * 8u;
+		k_pt_tri_shade<<<(int) (want < full ? want : full), kPtThreads, 0, st>>>(ctx->d_verts, ctx->d_flags, n_mat, ctx->n_tri, pt->d_tri_shade);
+		Y4_CUDA(ctx, cudaGetLastError());
+	}
+	sc.lights = pt->d_lights; sc.mats = pt->d_mats; sc.tri_shade = pt->d_tri_shade; sc.normals = pt->d_normals;
+	sc.lds.sigma = pt->d_sigma; sc.lds.offset = pt->d_offset; sc.lds.prime = pt->d_prime; sc.lds.inv_prime = pt->d_inv_prime; sc.lds.sigma_d = pt->d_sigma_d; sc.lds.magic = pt->d_magic;
 	// film (internal unless the caller installs buffers)
 	const size_t npx = (size_t) sc.width * sc.height;
 	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); pt->own_film_w = pt->own_film_rgba = nullptr;
@@ -348,8 +371,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	{
 		sc.aa_light_sample_multiplier = mult;
 		pt->max_light_samples = 1;
-		for(int i = 0; i < sc.n_lights; ++i) { const int ns = y4_light_num_samples(sc, sc.lights[i]); if(ns > pt->max_light_samples) pt->max_light_samples = ns; }
-		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_scene, &sc, sizeof(Y4PtScene), cudaMemcpyHostToDevice, st));
+		for(int i = 0; i < sc.n_lights; ++i) { const int ns = y4_light_num_samples(sc, pt->h_lights[i]); if(ns > pt->max_light_samples) pt->max_light_samples = ns; }
 	}
 	const uint64_t n_pix = pixel_list ? n_pixels : (uint64_t) sc.width * sc.height;
 	const uint32_t ns_local = shard_index < n_samples ? (uint32_t) ((n_samples - shard_index + shard_count - 1) / shard_count) : 0u;
@@ -375,11 +397,11 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	if(total < wave_size) wave_size = (uint32_t) (total ? total : 1);
 	{ const int rc = pt_alloc_wave(ctx, pt, wave_size); if(rc) return rc; }
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass_number;
-	const Y4PtScene *dsc = pt->d_scene;
+	const Y4PtScene &dsc = sc;
 	// the (light, sample) sequence of estimateAllDirectLight at the camera hit
 	std::vector<std::pair<int, int>> all_lk;
 	for(int l = 0; l < sc.n_lights; ++l)
-		for(int k = 0, ns = y4_light_num_samples(sc, sc.lights[l]); k < ns; ++k) all_lk.push_back(std::make_pair(l, k));
+		for(int k = 0, ns = y4_light_num_samples(sc, pt->h_lights[l]); k < ns; ++k) all_lk.push_back(std::make_pair(l, k));
 	const int max_ls = pt->max_light_samples;
 	// counter slots: [0..5] traversal visit counters (profile mode), then one per queue / trace launch
 	const uint64_t n_waves = total ? (total + wave_size - 1) / wave_size : 0;

@@ -91,6 +91,22 @@ Y4_HD float y4_halton_next(Y4Halton &h)
 	return y4_clamp01((float) h.value);
 }
 
+// Base-2 member of the sequence in closed form: the q-th y4_halton_next after y4_halton_start(2, start)
+// is the radical inverse of start + q.  Every intermediate of the recurrence is a dyadic rational with at
+// most 33 fractional bits (exact in fp64), and the 1e-10 guard in `r` never flips a comparison because the
+// compared quantities differ by 0 or by at least 2^-33 (1.16e-10).  tests/test_pt_cpu.py checks it against
+// the recurrence above (which is pinned to the reference by KATs).
+Y4_HD float y4_halton2_at(uint32_t start, uint32_t q)
+{
+	uint64_t n = (uint64_t) start + (uint64_t) q, r = 0;
+#if defined(__CUDA_ARCH__)
+	r = __brevll(n);
+#else
+	for(int k = 0; k < 64; ++k) { r = (r << 1) | (n & 1ull); n >>= 1; }
+#endif
+	return y4_clamp01((float) ((double) r * 5.421010862427522170037264e-20));     // 2^-64, exact scale
+}
+
 // ---- Faure-permuted Halton, 50 dimensions -------------------------------------------------------
 // Tables are generated (Faure's recursive construction, y4_faure.h) rather than transcribed;
 // the generated permutations and the 9-digit reciprocals are pinned by KATs from the reference.
@@ -100,9 +116,13 @@ struct Y4LdsTables
 	const uint16_t *offset;     // [50] start of dimension d in sigma
 	const uint16_t *prime;      // [50] base of dimension d   (1, 2, 3, 5, 7, ...)
 	const double *inv_prime;    // [50] reciprocal truncated to 9 decimals, as double
+	const double *sigma_d;      // sigma as doubles
+	const unsigned long long *magic;   // [50] floor(2^64 / prime) + 1
 };
 
-Y4_HD double y4_lds(const Y4LdsTables &tb, int dim, uint32_t n)
+// the reference's loop as written (Halton::lowDiscrepancySampling, halton.cc:403-441); kept as the
+// cross-check of the fast form below
+Y4_HD double y4_lds_loop(const Y4LdsTables &tb, int dim, uint32_t n)
 {
 	double value = 0.0;
 	const uint8_t *sigma = tb.sigma + tb.offset[dim];
@@ -113,6 +133,29 @@ Y4_HD double y4_lds(const Y4LdsTables &tb, int dim, uint32_t n)
 	while(n > 0)
 	{
 		value = xdadd(value, xdmul((double) sigma[n % base], factor));
+		dn = xdmul(dn, f);
+		n = (uint32_t) dn;
+		factor = xdmul(factor, f);
+	}
+	return value;
+}
+
+// Same arithmetic, cheaper digit extraction: n % base through an exact multiply-high (no integer
+// division), permutation values read as doubles.
+Y4_HD double y4_lds(const Y4LdsTables &tb, int dim, uint32_t n)
+{
+	double value = 0.0;
+	const double *sigma = tb.sigma_d + tb.offset[dim];
+	const uint32_t base = tb.prime[dim];
+	const unsigned long long magic = tb.magic[dim];
+	const uint32_t m_lo = (uint32_t) magic, m_hi = (uint32_t) (magic >> 32);
+	const double f = tb.inv_prime[dim];
+	double dn = (double) n;
+	double factor = f;
+	while(n > 0)
+	{
+		const uint32_t q = (uint32_t) (((uint64_t) n * m_hi + (((uint64_t) n * m_lo) >> 32)) >> 32);     // n / base
+		value = xdadd(value, xdmul(sigma[n - q * base], factor));
 		dn = xdmul(dn, f);
 		n = (uint32_t) dn;
 		factor = xdmul(factor, f);

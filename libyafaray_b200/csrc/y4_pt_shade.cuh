@@ -14,12 +14,25 @@
 #include "y4_pt_types.cuh"
 
 // ---- surface ---------------------------------------------------------------------------------
+// Per-triangle shading record, computed once per scene: the face normal of calculateNormal
+// (primitive_triangle.cc:92-95; fp32-deterministic, so hoisting it changes no bits) and the material index.
+Y4_HD float4 y4_tri_shade(const float *verts, const uint32_t *tri_flags, uint32_t n_mats, uint64_t prim)
+{
+	const float *v = verts + 9ull * prim;
+	const V3 a = v3(v[0], v[1], v[2]), b = v3(v[3], v[4], v[5]), c = v3(v[6], v[7], v[8]);
+	const V3 ng = xnormalize(xcross(xsub3(b, a), xsub3(c, a)));
+	uint32_t mat = tri_flags ? (tri_flags[prim] >> Y4_TRI_MAT_SHIFT) : 0u;
+	if(mat >= n_mats) mat = 0u;
+	float4 r; r.x = ng.x; r.y = ng.y; r.z = ng.z; r.w = y4_u2f(mat);
+	return r;
+}
+
 Y4_HD Y4Surf y4_surface(const Y4PtScene &sc, const V3 ray_o, const V3 ray_d, float t, float bu, float bv, int32_t prim)
 {
 	Y4Surf s;
-	const float *v = sc.verts + 9ull * (uint32_t) prim;
-	const V3 a = v3(v[0], v[1], v[2]), b = v3(v[3], v[4], v[5]), c = v3(v[6], v[7], v[8]);
-	s.ng = xnormalize(xcross(xsub3(b, a), xsub3(c, a)));            // calculateNormal, :92-95
+	const float4 ts = sc.tri_shade[(uint32_t) prim];
+	s.ng = v3(ts.x, ts.y, ts.z);
+	s.mat = y4_f2u(ts.w);
 	if(sc.normals)
 	{
 		const float *nn = sc.normals + 9ull * (uint32_t) prim;
@@ -30,8 +43,6 @@ Y4_HD Y4Surf y4_surface(const Y4PtScene &sc, const V3 ray_o, const V3 ray_d, flo
 	else s.n = s.ng;
 	s.p = xadd3(ray_o, xscale(ray_d, t));                            // ray.from_ + t * ray.dir_ (accelerator.cc:62)
 	y4_coords_system(s.n, s.nu, s.nv);
-	s.mat = sc.tri_flags ? (sc.tri_flags[prim] >> Y4_TRI_MAT_SHIFT) : 0u;
-	if(s.mat >= (uint32_t) sc.n_mats) s.mat = 0u;
 	return s;
 }
 Y4_HD V3 y4_face_forward(const V3 ng, const V3 n, const V3 incoming) { return xdot(ng, incoming) < 0.f ? xneg(n) : n; }

@@ -21,6 +21,8 @@ struct Y4PtWave
 	float *thr;            // [n*4] throughput
 	float *lcol;           // [n*4] emitted light picked up at the current vertex
 	float *acc_a, *acc_b;  // [n*4] per-light sums of the light-sample / BSDF-sample estimators
+	float *lsamp;          // [n*4] last light sample drawn for this pixel-sample: s1, s2, light, k (the reference draws
+	                       //       the same numbers at every vertex of a pixel-sample, see y4_light_sample_numbers)
 	Y4Ray *ray; Y4Hit *hit; Y4Hit *hit0;
 	Y4Ray *sray;           // [2n] shadow rays: slot 0 at [i], slot 1 at [n + i]
 	Y4Hit *shit;           // [2n]
@@ -34,18 +36,47 @@ struct Y4PtPass
 	int aa_pass;
 };
 
-Y4_HD C3 ld3(const float *p, uint32_t i) { return c3(p[4ull * i], p[4ull * i + 1], p[4ull * i + 2]); }
-Y4_HD void st3(float *p, uint32_t i, C3 c) { p[4ull * i] = c.r; p[4ull * i + 1] = c.g; p[4ull * i + 2] = c.b; }
-
-struct Y4PixelSampling { int x, y; uint32_t offset; uint32_t sample; float dx, dy; };   // PixelSamplingData + jitter
-
-Y4_HD Y4PixelSampling y4_pixel_sampling(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp)
+// 16-byte state accesses (one 128-bit load/store each)
+Y4_HD float4 ld4(const float *p, uint32_t i) { return *reinterpret_cast<const float4 *>(p + 4ull * i); }
+Y4_HD void st4(float *p, uint32_t i, float4 v) { *reinterpret_cast<float4 *>(p + 4ull * i) = v; }
+Y4_HD float4 f4(float x, float y, float z, float w) { float4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
+Y4_HD C3 ld3(const float *p, uint32_t i) { const float4 v = ld4(p, i); return c3(v.x, v.y, v.z); }
+Y4_HD void st3(float *p, uint32_t i, C3 c) { st4(p, i, f4(c.r, c.g, c.b, 0.f)); }     // lane 3 unused except in `col` (alpha)
+Y4_HD Y4Ray ld_ray(const Y4Ray *p, uint32_t i)
 {
-	Y4PixelSampling r;
-	r.x = sc.cx0 + (int) (pix % (uint32_t) sc.width);
-	r.y = sc.cy0 + (int) (pix / (uint32_t) sc.width);
+	const float4 a = reinterpret_cast<const float4 *>(p + i)[0], b = reinterpret_cast<const float4 *>(p + i)[1];
+	Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w; return r;
+}
+Y4_HD void st_ray(Y4Ray *p, uint32_t i, const Y4Ray &r)
+{
+	reinterpret_cast<float4 *>(p + i)[0] = f4(r.ox, r.oy, r.oz, r.tmin); reinterpret_cast<float4 *>(p + i)[1] = f4(r.dx, r.dy, r.dz, r.tmax);
+}
+Y4_HD Y4Hit ld_hit(const Y4Hit *p, uint32_t i)
+{
+	const float4 a = *reinterpret_cast<const float4 *>(p + i);
+	Y4Hit h; h.t = a.x; h.bu = a.y; h.bv = a.z; h.prim = (int32_t) y4_f2u(a.w); return h;
+}
+Y4_HD void st_hit(Y4Hit *p, uint32_t i, const Y4Hit &h) { *reinterpret_cast<float4 *>(p + i) = f4(h.t, h.bu, h.bv, y4_u2f((uint32_t) h.prim)); }
+
+// PixelSamplingData (integrator_tiled.cc:311-330): pixel, per-pixel hash offset, sample number
+struct Y4PixelId { int x, y; uint32_t offset; uint32_t sample; };
+Y4_HD Y4PixelId y4_pixel_id(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp)
+{
+	Y4PixelId r;
+	const uint32_t row = pix / (uint32_t) sc.width;
+	r.x = sc.cx0 + (int) (pix - row * (uint32_t) sc.width);
+	r.y = sc.cy0 + (int) row;
 	r.offset = y4_fnv32a((uint32_t) r.y * y4_fnv32a((uint32_t) r.x));
 	r.sample = ps.pass_offs + samp;
+	return r;
+}
+
+struct Y4PixelSampling { int x, y; uint32_t offset; uint32_t sample; float dx, dy; };   // + the sample's jitter inside the pixel
+Y4_HD Y4PixelSampling y4_pixel_sampling(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp)
+{
+	const Y4PixelId id = y4_pixel_id(sc, ps, pix, samp);
+	Y4PixelSampling r;
+	r.x = id.x; r.y = id.y; r.offset = id.offset; r.sample = id.sample;
 	r.dx = 0.5f; r.dy = 0.5f;
 	if(sc.aa_passes > 1)
 	{
@@ -74,17 +105,18 @@ Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py)
 // Elemental steps take the path's flag word in a register (`f`); the fused stage functions further
 // down load and store it once.  Shadow rays exist only for the slots whose Y4_PF_S0/S1 bit is set;
 // an untraced slot counts as unoccluded (no shadow casting, or an invalid sample with zero contribution).
+// State a stage always needs is loaded up front (independent 128-bit loads in flight together),
+// not behind the branches that consume it.
 
 // ---- step: camera ray ---------------------------------------------------------------------------
-Y4_HD Y4Ray y4_primary_ray(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
+Y4_HD Y4Ray y4_primary_ray(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp)
 {
-	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, pix, samp);
 	return y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy));
 }
 Y4_HD void y4_pt_gen(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
 {
-	W.ray[i] = y4_primary_ray(sc, W, ps, i);
-	W.flags[i] = 0u;
+	st_ray(W.ray, i, y4_primary_ray(sc, ps, W.pix[i], W.samp[i]));
 }
 
 struct Y4Vertex { Y4Surf sp; Y4PtMaterial m; V3 wo; };
@@ -102,22 +134,23 @@ Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 // returns true and fills `vx` when the camera ray hit a surface
 Y4_HD bool y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t &f, Y4Vertex &vx)
 {
-	const Y4Hit h = W.hit[i];
-	W.hit0[i] = h;
+	const Y4Hit h = ld_hit(W.hit, i);
+	const Y4Ray r = ld_ray(W.ray, i);
 	if(h.prim < 0)
 	{
 		const bool transp = sc.transp_background != 0;      // ray_level == 0
-		st3(W.col, i, transp ? c3f(0.f) : sc.background);
-		W.col[4ull * i + 3] = transp ? 0.f : 1.f;
+		const C3 bg = transp ? c3f(0.f) : sc.background;
+		st4(W.col, i, f4(bg.r, bg.g, bg.b, transp ? 0.f : 1.f));
 		f = 0u;
 		return false;
 	}
-	vx = y4_vertex(sc, W.ray[i], h);
+	st_hit(W.hit0, i, h);
+	vx = y4_vertex(sc, r, h);
 	C3 col = c3f(0.f);
 	if(vx.m.bsdf_flags & Y4_BSDF_EMIT) col = cadd(col, y4_mat_emit(vx.m, vx.sp, vx.wo));
-	st3(W.col, i, col);
-	W.col[4ull * i + 3] = 1.f;                                // recursiveRaytrace: alpha_count == 0 -> 1
+	st4(W.col, i, f4(col.r, col.g, col.b, 1.f));               // recursiveRaytrace: alpha_count == 0 -> alpha 1
 	st3(W.pcol, i, c3f(0.f));
+	st4(W.lsamp, i, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
 	f = Y4_PF_HIT0;
 	if(vx.m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
 	const uint32_t path_flags = sc.no_recursive ? (uint32_t) Y4_BSDF_ALL : (uint32_t) Y4_BSDF_DIFFUSE;
@@ -136,16 +169,31 @@ Y4_HD int y4_light_num_samples(const Y4PtScene &sc, const Y4PtLight &L)
 Y4_HD bool y4_direct_active(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t f, bool all_lights, int light, int k, int &l, int &num_samples)
 {
 	if(!(f & Y4_PF_DIRECT) || (!all_lights && !(f & Y4_PF_ALIVE))) return false;
-	l = all_lights ? light : (int) W.lnum[i];
+	l = all_lights ? light : (sc.n_lights > 1 ? (int) W.lnum[i] : 0);
 	num_samples = y4_light_num_samples(sc, sc.lights[l]);
 	return k < num_samples;
+}
+
+// The pair of numbers areaLightSampleLight / areaLightSampleMaterial use for sample k of light l
+// (integrator_montecarlo.cc:398-404: Halton(2) and Halton(3) started at num_samples * sample + offset + l * 4567 - 1,
+// advanced k + 1 times).  They depend on the pixel-sample, the light and k only -- not on the vertex -- so the last
+// pair is kept in W.lsamp and reused down the path.
+Y4_HD void y4_light_sample_numbers(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l, int k, int num_samples, float4 cache, float &s1, float &s2)
+{
+	if(y4_f2u(cache.z) == (uint32_t) l && y4_f2u(cache.w) == (uint32_t) k) { s1 = cache.x; s2 = cache.y; return; }
+	const Y4PixelId s = y4_pixel_id(sc, ps, W.pix[i], W.samp[i]);
+	const uint32_t offs = (uint32_t) num_samples * s.sample + s.offset + (uint32_t) l * 4567u;
+	s1 = y4_halton2_at(offs - 1u, (uint32_t) k + 1u);
+	Y4Halton h3 = y4_halton_start(3u, offs - 1u);
+	for(int q = 0; q <= k; ++q) s2 = y4_halton_next(h3);
+	st4(W.lsamp, i, f4(s1, s2, y4_u2f((uint32_t) l), y4_u2f((uint32_t) k)));
 }
 
 // ---- step: k-th sample of one light at vertex `vx` -------------------------------------------------
 // all_lights: vertex = camera hit (estimateAllDirectLight, light index given);
 // otherwise : vertex = current path vertex, light = W.lnum[i] (estimateOneDirectLight).
 // Returns the mask of shadow-ray slots written (bit q -> W.sray[q * n + i]).
-Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, bool all_lights, int light, int k, const Y4Vertex &vx)
+Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, bool all_lights, int light, int k, const Y4Vertex &vx, float4 cache)
 {
 	const uint32_t n = W.n;
 	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1);
@@ -153,13 +201,7 @@ Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return 0u;
 	const Y4PtLight &L = sc.lights[l];
 	float s1 = 0.f, s2 = 0.f;
-	if(L.type != Y4GPU_LIGHT_POINT)
-	{
-		const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
-		const uint32_t offs = (uint32_t) num_samples * s.sample + s.offset + (uint32_t) l * 4567u;
-		Y4Halton h2 = y4_halton_start(2u, offs - 1u), h3 = y4_halton_start(3u, offs - 1u);
-		for(int q = 0; q <= k; ++q) { s1 = y4_halton_next(h2); s2 = y4_halton_next(h3); }
-	}
+	if(L.type != Y4GPU_LIGHT_POINT) y4_light_sample_numbers(sc, W, ps, i, l, k, num_samples, cache, s1, s2);
 	Y4DirectOut out;
 	y4_direct_sample(sc, L, vx.m, vx.sp, vx.wo, s1, s2, out);
 	const bool cast = L.cast_shadows && vx.m.receive_shadows;
@@ -168,7 +210,7 @@ Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 	{
 		st3(W.scontrib, q * n + i, out.contrib[q]);           // zero when the sample is invalid
 		if(!out.valid[q] || !cast) continue;
-		W.sray[q * n + i] = out.ray[q];
+		st_ray(W.sray, q * n + i, out.ray[q]);
 		mask |= 1u << q;
 	}
 	if(mask & 1u) f |= Y4_PF_S0;
@@ -182,12 +224,18 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 	const uint32_t n = W.n;
 	int l, num_samples;
 	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return;
+	// everything this step can need, requested together
+	const float4 c0 = ld4(W.scontrib, i), c1 = ld4(W.scontrib, n + i);
+	const int32_t p0 = (f & Y4_PF_S0) ? W.shit[i].prim : -1, p1 = (f & Y4_PF_S1) ? W.shit[n + i].prim : -1;
+	const float4 base = all_lights ? ld4(W.col, i) : ld4(W.pcol, i);
+	const float4 thr4 = all_lights ? f4(0.f, 0.f, 0.f, 0.f) : ld4(W.thr, i);
+	const float4 lc4 = all_lights ? f4(0.f, 0.f, 0.f, 0.f) : ld4(W.lcol, i);
 	const Y4PtLight &L = sc.lights[l];
 	// running sums over the light's samples live in acc_a/acc_b only between samples (k > 0)
 	C3 a = c3f(0.f), b = c3f(0.f);
 	if(k > 0) { a = ld3(W.acc_a, i); b = ld3(W.acc_b, i); }
-	if(!(f & Y4_PF_S0) || W.shit[i].prim < 0) a = cadd(a, ld3(W.scontrib, i));
-	if(!(f & Y4_PF_S1) || W.shit[n + i].prim < 0) b = cadd(b, ld3(W.scontrib, n + i));
+	if(p0 < 0) a = cadd(a, c3(c0.x, c0.y, c0.z));
+	if(p1 < 0) b = cadd(b, c3(c1.x, c1.y, c1.z));
 	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1);
 	if(k < num_samples - 1) { st3(W.acc_a, i, a); st3(W.acc_b, i, b); return; }
 	// last sample of this light: doLightEstimation's result
@@ -199,34 +247,43 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 		dl = cadd(dl, cscale(a, inv));
 		dl = cadd(dl, cscale(b, inv));
 	}
-	if(all_lights) st3(W.col, i, cadd(ld3(W.col, i), dl));                     // estimateAllDirectLight: col += ...
+	if(all_lights)                                                             // estimateAllDirectLight: col += ...
+	{
+		const C3 c = cadd(c3(base.x, base.y, base.z), dl);
+		st4(W.col, i, f4(c.r, c.g, c.b, base.w));
+	}
 	else
 	{
 		// estimateOneDirectLight: ... * num_lights; then "lcol += col_emit" (first vertex) and path_col += lcol * throughput
 		C3 lcol = cscale(dl, (float) sc.n_lights);
-		lcol = cadd(lcol, ld3(W.lcol, i));
-		st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, ld3(W.thr, i))));
+		lcol = cadd(lcol, c3(lc4.x, lc4.y, lc4.z));
+		st3(W.pcol, i, cadd(c3(base.x, base.y, base.z), cmul(lcol, c3(thr4.x, thr4.y, thr4.z))));
 		f &= ~(uint32_t) Y4_PF_DIRECT;
 	}
 }
 
 // ---- step: BSDF sample that extends sub-path `sub` at bounce `depth` (integrate(), :163-231) --------
-// returns true when W.ray[i] holds the next ray of the path
+// FIRST: depth == 0 (the vertex is the camera hit).  Returns true when W.ray[i] holds the next ray of the path.
+template<bool FIRST>
 Y4_HD bool y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, int depth, int sub)
 {
-	if(depth == 0)
+	const uint32_t pix = W.pix[i], samp = W.samp[i];
+	const Y4Hit h = FIRST ? ld_hit(W.hit0, i) : ld_hit(W.hit, i);
+	Y4Ray r;
+	float4 thr4 = f4(0.f, 0.f, 0.f, 0.f);
+	if(!FIRST) { r = ld_ray(W.ray, i); thr4 = ld4(W.thr, i); }
+	if(FIRST)
 	{
 		f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIFF1 | Y4_PF_DIRECT);
 		if(!(f & Y4_PF_PATHS)) return false;
+		r = y4_primary_ray(sc, ps, pix, samp);
 	}
 	else if(!(f & Y4_PF_ALIVE)) return false;
-	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+	const Y4PixelId s = y4_pixel_id(sc, ps, pix, samp);
 	const uint32_t offs = (uint32_t) sc.n_paths * s.sample + s.offset + (uint32_t) sub;
-	const Y4Ray r = depth == 0 ? y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy)) : W.ray[i];
-	const Y4Hit h = depth == 0 ? W.hit0[i] : W.hit[i];
 	const Y4Vertex vx = y4_vertex(sc, r, h);
 	float s1, s2; uint32_t sflags;
-	if(depth == 0)
+	if(FIRST)
 	{
 		s1 = y4_ri_vdc(offs, 0u);
 		s2 = (float) y4_lds(sc.lds, 2, offs);
@@ -242,14 +299,14 @@ Y4_HD bool y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4P
 	float w = 0.f, pdf; bool sampled;
 	C3 scol = y4_mat_sample(vx.m, vx.sp, vx.wo, s1, s2, sflags, wi, w, pdf, sampled);
 	scol = cscale(scol, w);
-	if(depth == 0) st3(W.thr, i, scol);
+	if(FIRST) st3(W.thr, i, scol);
 	else
 	{
 		if(cblack(scol)) { f &= ~(uint32_t) Y4_PF_ALIVE; return false; }
-		st3(W.thr, i, cmul(ld3(W.thr, i), scol));
+		st3(W.thr, i, cmul(c3(thr4.x, thr4.y, thr4.z), scol));
 	}
 	if(!sampled) { f &= ~(uint32_t) Y4_PF_ALIVE; return false; }   // reference: direction undefined
-	W.ray[i] = y4_mk_ray(vx.sp.p, sc.ray_min_dist, wi, -1.f);
+	st_ray(W.ray, i, y4_mk_ray(vx.sp.p, sc.ray_min_dist, wi, -1.f));
 	f |= Y4_PF_ALIVE;
 	return true;
 }
@@ -258,11 +315,15 @@ Y4_HD bool y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4P
 // returns true (and fills vx) when the vertex wants a one-light estimate (Y4_PF_DIRECT set, W.lnum chosen)
 Y4_HD bool y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, int depth, int sub, Y4Vertex &vx)
 {
+	const Y4Hit h = ld_hit(W.hit, i);
+	const Y4Ray r = ld_ray(W.ray, i);
+	const float4 thr4 = ld4(W.thr, i);
+	const uint32_t pix = W.pix[i], samp = W.samp[i];
 	if(!(f & Y4_PF_ALIVE)) return false;
-	const Y4Hit h = W.hit[i];
 	if(h.prim < 0) { f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return false; }     // hit background: continue / break
-	vx = y4_vertex(sc, W.ray[i], h);
+	vx = y4_vertex(sc, r, h);
 	const Y4PtMaterial &m = vx.m;
+	C3 thr = c3(thr4.x, thr4.y, thr4.z);
 	C3 emit = c3f(0.f);
 	bool direct;
 	if(depth == 0)
@@ -277,12 +338,12 @@ Y4_HD bool y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 		if(depth > sc.rr_min_bounces)
 		{
 			// the reference draws from a rand()-seeded per-tile generator (not reproducible); documented substitute
-			const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
+			const Y4PixelId s = y4_pixel_id(sc, ps, pix, samp);
 			const float random_value = y4_hash_uniform(sc.rr_seed ^ s.offset, s.sample, (uint32_t) (sub * 64 + depth));
-			C3 thr = ld3(W.thr, i);
 			const float probability = cmax(thr);
 			if(probability <= 0.f || probability < random_value) { f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return false; }
-			st3(W.thr, i, cscale(thr, xdiv(1.f, probability)));
+			thr = cscale(thr, xdiv(1.f, probability));
+			st3(W.thr, i, thr);
 		}
 	}
 	if(sc.n_lights == 0) direct = false;
@@ -290,18 +351,20 @@ Y4_HD bool y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 	{
 		// light choice of estimateOneDirectLight: Halton(2) at base offset + a per-call counter.  The
 		// reference counter is per CPU thread (call-order dependent); here it is a per-vertex index.
-		const Y4PixelSampling s = y4_pixel_sampling(sc, ps, W.pix[i], W.samp[i]);
-		const uint32_t corr = (W.pix[i] * 1009u + s.sample) * (uint32_t) (sc.bounces * sc.n_paths) + (uint32_t) (sub * sc.bounces + depth);
-		Y4Halton h2 = y4_halton_start(2u, sc.base_sampling_offset + corr - 1u);
-		const int lnum = (int) xmul(y4_halton_next(h2), (float) sc.n_lights);
-		W.lnum[i] = (uint32_t) (lnum < sc.n_lights - 1 ? lnum : sc.n_lights - 1);
+		// With one light every draw picks light 0 (min(int(h * 1), 0)): nothing to compute or store.
+		if(sc.n_lights > 1)
+		{
+			const uint32_t corr = (pix * 1009u + ps.pass_offs + samp) * (uint32_t) (sc.bounces * sc.n_paths) + (uint32_t) (sub * sc.bounces + depth);
+			const int lnum = (int) xmul(y4_halton2_at(sc.base_sampling_offset + corr - 1u, 1u), (float) sc.n_lights);
+			W.lnum[i] = (uint32_t) (lnum < sc.n_lights - 1 ? lnum : sc.n_lights - 1);
+		}
 		st3(W.lcol, i, emit);
 		f |= Y4_PF_DIRECT;
 		return true;
 	}
 	// lcol = 0 (* num_lights) + emit;  path_col += lcol * throughput
 	const C3 lcol = cadd(c3f(0.f), emit);
-	st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, ld3(W.thr, i))));
+	st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, thr)));
 	f &= ~(uint32_t) Y4_PF_DIRECT;
 	return false;
 }
@@ -319,7 +382,7 @@ Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4
 	uint32_t push = 0u;
 	if(y4_pt_primary(sc, W, i, f, vx))
 	{
-		if(l0 >= 0) push |= y4_pt_direct(sc, W, ps, i, f, true, l0, 0, vx);
+		if(l0 >= 0) push |= y4_pt_direct(sc, W, ps, i, f, true, l0, 0, vx, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
 		if(f & (Y4_PF_DIRECT | Y4_PF_PATHS)) push |= Y4_PUSH_PATH;
 	}
 	W.flags[i] = f;
@@ -330,14 +393,15 @@ Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4
 Y4_HD uint32_t y4_stage_direct_step(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, bool all_lights, int l_prev, int k_prev, int l, int k)
 {
 	uint32_t f = W.flags[i];
+	const float4 cache = ld4(W.lsamp, i);
 	y4_pt_direct_resolve(sc, W, i, f, all_lights, l_prev, k_prev);
 	uint32_t push = 0u;
 	int ll, ns;
 	if(y4_direct_active(sc, W, i, f, all_lights, l, k, ll, ns))
 	{
-		const Y4Ray r = all_lights ? y4_primary_ray(sc, W, ps, i) : W.ray[i];
-		const Y4Vertex vx = y4_vertex(sc, r, all_lights ? W.hit0[i] : W.hit[i]);
-		push = y4_pt_direct(sc, W, ps, i, f, all_lights, l, k, vx);
+		const Y4Ray r = all_lights ? y4_primary_ray(sc, ps, W.pix[i], W.samp[i]) : ld_ray(W.ray, i);
+		const Y4Vertex vx = y4_vertex(sc, r, all_lights ? ld_hit(W.hit0, i) : ld_hit(W.hit, i));
+		push = y4_pt_direct(sc, W, ps, i, f, all_lights, l, k, vx, cache);
 	}
 	W.flags[i] = f;
 	return push;
@@ -348,7 +412,7 @@ Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 {
 	uint32_t f = W.flags[i];
 	if(l_last >= 0) y4_pt_direct_resolve(sc, W, i, f, true, l_last, k_last);
-	const bool go = y4_pt_bounce_sample(sc, W, ps, i, f, 0, sub);
+	const bool go = y4_pt_bounce_sample<true>(sc, W, ps, i, f, 0, sub);
 	W.flags[i] = f;
 	return go ? (uint32_t) Y4_PUSH_PATH : 0u;
 }
@@ -357,9 +421,10 @@ Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 Y4_HD uint32_t y4_stage_vertex(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub)
 {
 	uint32_t f = W.flags[i];
+	const float4 cache = ld4(W.lsamp, i);
 	Y4Vertex vx;
 	uint32_t push = 0u;
-	if(y4_pt_bounce_hit(sc, W, ps, i, f, depth, sub, vx)) push = y4_pt_direct(sc, W, ps, i, f, false, -1, 0, vx);
+	if(y4_pt_bounce_hit(sc, W, ps, i, f, depth, sub, vx)) push = y4_pt_direct(sc, W, ps, i, f, false, -1, 0, vx, cache);
 	W.flags[i] = f;
 	return push;
 }
@@ -370,7 +435,7 @@ Y4_HD uint32_t y4_stage_extend(const Y4PtScene &sc, const Y4PtWave &W, const Y4P
 	uint32_t f = W.flags[i];
 	if(k_last >= 0) y4_pt_direct_resolve(sc, W, i, f, false, -1, k_last);
 	bool go = false;
-	if(depth + 1 < sc.bounces) go = y4_pt_bounce_sample(sc, W, ps, i, f, depth + 1, sub);
+	if(depth + 1 < sc.bounces) go = y4_pt_bounce_sample<false>(sc, W, ps, i, f, depth + 1, sub);
 	W.flags[i] = f;
 	return go ? (uint32_t) Y4_PUSH_PATH : 0u;
 }
@@ -386,8 +451,9 @@ Y4_HD int y4_round_to_int(double v) { return (int) (v + (0.5 - 1.4e-11)); }     
 Y4_HD void y4_pt_finish_splat(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, float *film_w, float *film_rgba)
 {
 	const uint32_t f = W.flags[i];
-	C3 col = ld3(W.col, i);
-	float alpha = W.col[4ull * i + 3];
+	const float4 col4 = ld4(W.col, i);
+	C3 col = c3(col4.x, col4.y, col4.z);
+	float alpha = col4.w;
 	if(f & Y4_PF_PATHS) col = cadd(col, cdiv(ld3(W.pcol, i), (float) (sc.n_paths > 1 ? sc.n_paths : 1)));
 	if(alpha > 1.f) alpha = 1.f;
 	if(sc.clamp_samples > 0.f)      // Rgb::clampProportionalRgb (color.h:415-445)

@@ -1,6 +1,8 @@
 // Device-side scene description and per-path state of the wavefront path tracer.
-// Everything is derived on the host (y4_pt_host.cpp) from the parameter-level C-ABI structs with
-// the reference's own fp32 operation order, then uploaded once per y4gpu_pt_set_scene.
+// Everything is derived on the host (y4_pt_host.h) from the parameter-level C-ABI structs with
+// the reference's own fp32 operation order.  Y4PtScene travels to every kernel by value (kernel
+// parameter space = constant bank); the arrays behind its pointers are uploaded once per
+// y4gpu_pt_set_scene.
 #pragma once
 #include "y4_common.cuh"
 #include "y4_pt_sampling.cuh"
@@ -75,10 +77,9 @@ struct Y4PtScene
 	float filter_table[Y4_FILTER_TABLE * Y4_FILTER_TABLE];
 	// scene content
 	int n_lights, n_mats;
-	Y4PtLight lights[Y4_PT_MAX_LIGHTS];
-	const Y4PtMaterial *mats;       // device array
-	const float *verts;             // [n_tri * 9] world-space vertices in primitive order
-	const uint32_t *tri_flags;      // [n_tri] or null (material = flags >> 8)
+	const Y4PtLight *lights;        // [n_lights]
+	const Y4PtMaterial *mats;       // [n_mats]
+	const float4 *tri_shade;        // [n_tri] geometric normal (xyz) + material index (w, as int bits), see y4_tri_shade
 	const float *normals;           // [n_tri * 9] exported vertex normals or null
 	Y4LdsTables lds;                // Faure tables (device pointers)
 };

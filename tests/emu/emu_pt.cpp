@@ -62,24 +62,27 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	derive_film(*params, sc);
 	sc.n_lights = (int) n_light; sc.n_mats = (int) n_mat;
 	int max_ls = 1;
-	for(uint32_t i = 0; i < n_light; ++i) { sc.lights[i] = derive_light(lights[i]); const int ns = y4_light_num_samples(sc, sc.lights[i]); if(ns > max_ls) max_ls = ns; }
+	std::vector<Y4PtLight> hl(n_light);
+	for(uint32_t i = 0; i < n_light; ++i) { hl[i] = derive_light(lights[i]); const int ns = y4_light_num_samples(sc, hl[i]); if(ns > max_ls) max_ls = ns; }
+	std::vector<float4> tri_shade(n_tri);
+	for(int t = 0; t < n_tri; ++t) tri_shade[t] = y4_tri_shade(verts, flags, n_mat, (uint64_t) t);
 	std::vector<Y4PtMaterial> hm(n_mat);
 	for(uint32_t i = 0; i < n_mat; ++i) hm[i] = derive_material(mats[i]);
-	sc.mats = hm.data(); sc.verts = verts; sc.tri_flags = flags; sc.normals = normals;
-	sc.lds.sigma = fh.sigma.data(); sc.lds.offset = fh.offset; sc.lds.prime = fh.prime; sc.lds.inv_prime = fh.inv_prime;
+	sc.lights = hl.data(); sc.mats = hm.data(); sc.tri_shade = tri_shade.data(); sc.normals = normals;
+	sc.lds.sigma = fh.sigma.data(); sc.lds.offset = fh.offset; sc.lds.prime = fh.prime; sc.lds.inv_prime = fh.inv_prime; sc.lds.sigma_d = fh.sigma_d.data(); sc.lds.magic = fh.magic;
 
 	// same pixel-sample enumeration as k_pt_fill (y4_pt.cu)
 	const uint32_t ns_local = shard_index < n_samples ? (uint32_t) ((n_samples - shard_index + shard_count - 1) / shard_count) : 0u;
 	const uint32_t n = (uint32_t) sc.width * sc.height * ns_local;
 	if(n == 0) return 0;
 	std::vector<uint32_t> pix(n), samp(n), fl(n), lnum(n);
-	std::vector<float> col(4ull * n), pcol(4ull * n), thr(4ull * n), lcol(4ull * n), acc_a(4ull * n), acc_b(4ull * n), scontrib(8ull * n);
+	std::vector<float4> col(n), pcol(n), thr(n), lcol(n), acc_a(n), acc_b(n), lsamp(n), scontrib(2ull * n);
 	std::vector<Y4Ray> ray(n), sray(2ull * n);
 	std::vector<Y4Hit> hit(n), hit0(n), shit(2ull * n);
 	Y4PtWave W;
 	W.n = n; W.pix = pix.data(); W.samp = samp.data(); W.flags = fl.data(); W.lnum = lnum.data();
-	W.col = col.data(); W.pcol = pcol.data(); W.thr = thr.data(); W.lcol = lcol.data(); W.acc_a = acc_a.data(); W.acc_b = acc_b.data();
-	W.ray = ray.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = scontrib.data();
+	W.col = &col[0].x; W.pcol = &pcol[0].x; W.thr = &thr[0].x; W.lcol = &lcol[0].x; W.acc_a = &acc_a[0].x; W.acc_b = &acc_b[0].x; W.lsamp = &lsamp[0].x;
+	W.ray = ray.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = &scontrib[0].x;
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
 	for(uint32_t i = 0; i < n; ++i) { pix[i] = i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
 	// same stage sequence as y4gpu_pt_render_pass (y4_pt.cu), queues as vectors
@@ -87,7 +90,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	trace(bvh, Y4_TRACE_CLOSEST, W.ray, nullptr, n, W.hit);
 	std::vector<std::pair<int, int>> all_lk;
 	for(int l = 0; l < sc.n_lights; ++l)
-		for(int k = 0; k < y4_light_num_samples(sc, sc.lights[l]); ++k) all_lk.push_back(std::make_pair(l, k));
+		for(int k = 0; k < y4_light_num_samples(sc, hl[l]); ++k) all_lk.push_back(std::make_pair(l, k));
 	std::vector<uint32_t> q_hit0, q_shadow, q_cur, q_next;
 	for(uint32_t i = 0; i < n; ++i) push(y4_stage_primary(sc, W, ps, i, all_lk.empty() ? -1 : all_lk[0].first), i, n, &q_hit0, &q_shadow);
 	for(size_t j = 0; j < all_lk.size(); ++j)

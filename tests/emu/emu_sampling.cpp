@@ -7,11 +7,14 @@ static Y4FaureHost g_faure = y4_faure_build();
 static Y4LdsTables tables()
 {
 	Y4LdsTables t; t.sigma = g_faure.sigma.data(); t.offset = g_faure.offset; t.prime = g_faure.prime; t.inv_prime = g_faure.inv_prime;
+	t.sigma_d = g_faure.sigma_d.data(); t.magic = g_faure.magic;
 	return t;
 }
 
 extern "C" {
 double emu_lds(int dim, uint32_t n) { return y4_lds(tables(), dim, n); }
+double emu_lds_loop(int dim, uint32_t n) { return y4_lds_loop(tables(), dim, n); }
+float emu_halton2_at(uint32_t start, uint32_t q) { return y4_halton2_at(start, q); }
 void emu_ri(uint32_t i, uint32_t r, float *out3, uint32_t *fnv)
 {
 	out3[0] = y4_ri_vdc(i, r); out3[1] = y4_ri_s(i, r); out3[2] = y4_ri_lp(i, r); *fnv = y4_fnv32a(i);

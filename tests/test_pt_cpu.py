@@ -150,3 +150,28 @@ def test_sampling_kats():
         E.emu_coshemi(n3, C.c_float(f[3]), C.c_float(f[4]), o9)
         bad += [int(np.float32(x).view(np.uint32)) for x in o9] != row[5:]
     assert bad <= 2, bad
+
+
+def test_fast_sampling_forms_equal_the_pinned_recurrences():
+    """The cheaper forms used on the device (multiply-high digit extraction in the Faure-Halton loop, closed-form base-2
+    Halton) are bit-identical to the loop forms that the KATs above pin to the reference."""
+    import ctypes as C
+
+    E = helpers.emu()
+    E.emu_lds.restype = C.c_double
+    E.emu_lds_loop.restype = C.c_double
+    E.emu_halton2_at.restype = C.c_float
+    rng = np.random.default_rng(5)
+    ns = np.concatenate([rng.integers(0, 2 ** 32, 1500, dtype=np.uint64), [0, 1, 2, 2 ** 32 - 1, 2 ** 31, 3 ** 20, 3 ** 20 - 1, 229 * 229 * 229]]).astype(np.uint32)
+    for dim in list(range(1, 50)):
+        for n in ns[dim::7]:
+            a, b = E.emu_lds(C.c_int(dim), C.c_uint32(int(n))), E.emu_lds_loop(C.c_int(dim), C.c_uint32(int(n)))
+            assert np.float64(a).view(np.uint64) == np.float64(b).view(np.uint64), (dim, n)
+    o = (C.c_float * 5)()
+    starts = np.concatenate([rng.integers(0, 2 ** 32, 3000, dtype=np.uint64), [0, 1, 2 ** 32 - 1, 2 ** 32 - 2, 2 ** 32 - 5, 2 ** 31 - 1, 2 ** 31, 0x55555555, 0xAAAAAAAA],
+                             2 ** rng.integers(1, 32, 64, dtype=np.uint64) - 1]).astype(np.uint32)
+    for s in starts:
+        E.emu_halton(C.c_uint32(2), C.c_uint32(int(s)), 5, o)
+        for q in range(5):
+            got = E.emu_halton2_at(C.c_uint32(int(s)), C.c_uint32(q + 1))
+            assert np.float32(got).view(np.uint32) == np.float32(o[q]).view(np.uint32), (s, q)
