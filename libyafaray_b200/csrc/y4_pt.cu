@@ -18,6 +18,7 @@ struct Y4Pt
 	bool scene_set = false;
 	y4gpu_pt_params params = {};
 	int max_light_samples = 1;
+	int stage_min_blocks = 2;
 	// film
 	float *d_film_w = nullptr, *d_film_rgba = nullptr;      // in use
 	float *own_film_w = nullptr, *own_film_rgba = nullptr;  // owned (when the caller gave none)
@@ -47,7 +48,7 @@ namespace {
 
 constexpr int kPtThreads = 256;
 
-enum { kStPrimary, kStDirectStep, kStStart, kStVertex, kStExtend };
+enum { kStPrimary, kStDirectStep, kStStart, kStPath };
 struct StageArgs { int all_lights, l_prev, k_prev, l, k, depth, sub; };
 struct StageQueues
 {
@@ -69,8 +70,8 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_gen(const __grid_constant__ Y
 	}
 }
 
-template<int STAGE>
-__global__ void __launch_bounds__(kPtThreads) k_pt_stage(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, StageArgs a, StageQueues Q)
+template<int STAGE, int MINB>
+__global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, StageArgs a, StageQueues Q)
 {
 	const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
 	const uint32_t count = Q.in_q ? *Q.in_count : W.n;
@@ -85,10 +86,9 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_stage(const __grid_constant__
 			if(STAGE == kStPrimary) push = y4_stage_primary(sc, W, ps, i, a.l);
 			else if(STAGE == kStDirectStep) push = y4_stage_direct_step(sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
 			else if(STAGE == kStStart) push = y4_stage_start(sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
-			else if(STAGE == kStVertex) push = y4_stage_vertex(sc, W, ps, i, a.depth, a.sub);
-			else push = y4_stage_extend(sc, W, ps, i, a.depth, a.sub, a.k_prev);
+			else push = y4_stage_path(sc, W, ps, i, a.depth, a.sub, a.k_prev);
 		}
-		if(STAGE == kStPrimary || STAGE == kStDirectStep || STAGE == kStVertex)
+		if(STAGE == kStPrimary || STAGE == kStDirectStep || STAGE == kStPath)
 		{
 			const uint32_t m0 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S0), m1 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S1);
 			if(m0 | m1)
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_stage(const __grid_constant__
 				if(push & Y4_PUSH_S1) Q.sh_q[at + __popc(m0) + __popc(m1 & lt_mask)] = W.n + i;
 			}
 		}
-		if(STAGE == kStPrimary || STAGE == kStStart || STAGE == kStExtend)
+		if(STAGE == kStPrimary || STAGE == kStStart || STAGE == kStPath)
 		{
 			const uint32_t mp = __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH);
 			if(mp)
@@ -124,6 +124,15 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_splat(const __grid_constant__
 	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_finish_splat(sc, W, ps, i, film_w, film_rgba);
 }
 
+// register budget of the stage kernels: MINB resident CTAs per SM (2: no cap, 3: 80 registers, 4: 64 registers)
+template<int STAGE>
+void launch_stage(int minb, int grid, cudaStream_t st, const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, const StageArgs &a, const StageQueues &Q)
+{
+	if(minb >= 4) k_pt_stage<STAGE, 4><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+	else if(minb == 3) k_pt_stage<STAGE, 3><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+	else k_pt_stage<STAGE, 2><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+}
+
 inline int pt_grid(const y4gpu_ctx *ctx, uint32_t n)
 {
 	const uint32_t want = (n + kPtThreads - 1) / kPtThreads, full = (uint32_t) ctx->sm_count * 8u;
@@ -141,7 +150,7 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt *pt, uint32_t cap)
 	if(cap <= pt->cap) return Y4GPU_OK;
 	pt_free_wave(pt);
 	const size_t n = cap;
-	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 32 + 16 + 16 /*ray hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/
+	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 16 /*pthr*/ + 2 * 32 + 16 + 16 /*ray x2 hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/
 	                          + 16 /*lsamp*/ + 5 * 4 /*queues*/) + 512;
 	Y4_CUDA(ctx, cudaMalloc(&pt->wave_mem, bytes));
 	char *p = (char *) pt->wave_mem;
@@ -149,7 +158,7 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt *pt, uint32_t cap)
 	Y4PtWave &W = pt->wave;
 	W.col = (float *) take(n * 16); W.pcol = (float *) take(n * 16); W.thr = (float *) take(n * 16); W.lcol = (float *) take(n * 16);
 	W.acc_a = (float *) take(n * 16); W.acc_b = (float *) take(n * 16); W.lsamp = (float *) take(n * 16);
-	W.ray = (Y4Ray *) take(n * 32); W.hit = (Y4Hit *) take(n * 16); W.hit0 = (Y4Hit *) take(n * 16);
+	W.ray = (Y4Ray *) take(n * 32); W.ray_next = (Y4Ray *) take(n * 32); W.pthr = (float *) take(n * 16); W.hit = (Y4Hit *) take(n * 16); W.hit0 = (Y4Hit *) take(n * 16);
 	W.sray = (Y4Ray *) take(2 * n * 32); W.shit = (Y4Hit *) take(2 * n * 16); W.scontrib = (float *) take(2 * n * 16);
 	W.pix = (uint32_t *) take(n * 4); W.samp = (uint32_t *) take(n * 4); W.flags = (uint32_t *) take(n * 4); W.lnum = (uint32_t *) take(n * 4);
 	pt->q_hit0 = (uint32_t *) take(n * 4); pt->q_path[0] = (uint32_t *) take(n * 4); pt->q_path[1] = (uint32_t *) take(n * 4); pt->q_shadow = (uint32_t *) take(2 * n * 4);
@@ -202,6 +211,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		if(lights[i].type != Y4GPU_LIGHT_POINT && lights[i].type != Y4GPU_LIGHT_AREA) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	if(!ctx->pt) ctx->pt = new Y4Pt;
+	if(const char *e = getenv("Y4GPU_PT_MIN_BLOCKS")) ctx->pt->stage_min_blocks = atoi(e);
 	Y4Pt *pt = ctx->pt;
 	if(!pt->ev0) { Y4_CUDA(ctx, cudaEventCreate(&pt->ev0)); Y4_CUDA(ctx, cudaEventCreate(&pt->ev1)); }
 	cudaStream_t st = ctx->stream;
@@ -405,7 +415,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	const int max_ls = pt->max_light_samples;
 	// counter slots: [0..5] traversal visit counters (profile mode), then one per queue / trace launch
 	const uint64_t n_waves = total ? (total + wave_size - 1) / wave_size : 0;
-	const size_t per_wave = 4 + 2 * all_lk.size() + (size_t) sc.n_paths * (2 + (size_t) sc.bounces * (4 + 2 * (size_t) max_ls));
+	const size_t per_wave = 4 + 2 * all_lk.size() + (size_t) sc.n_paths * (2 + ((size_t) sc.bounces + 1) * (4 + 2 * (size_t) max_ls));
 	const size_t need = 8 + n_waves * per_wave;
 	if(need > pt->counters_cap)
 	{
@@ -452,46 +462,51 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		uint32_t *n_hit0 = new_queue_count(-1);
 		Q.out_q = pt->q_hit0; Q.out_count = n_hit0; Q.sh_q = pt->q_shadow; Q.sh_count = new_queue_count(1);
 		a.l = all_lk.empty() ? -1 : all_lk[0].first;
-		Y4_PT_LAUNCH(3, k_pt_stage<kStPrimary><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
+		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
 		for(size_t j = 0; j < all_lk.size(); ++j)
 		{
 			Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
 			if(j + 1 == all_lk.size()) break;          // the last sample is resolved by the start stage
 			Q.in_q = pt->q_hit0; Q.in_count = n_hit0; Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
 			a.all_lights = 1; a.l_prev = all_lk[j].first; a.k_prev = all_lk[j].second; a.l = all_lk[j + 1].first; a.k = all_lk[j + 1].second;
-			Y4_PT_LAUNCH(4, k_pt_stage<kStDirectStep><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
+			Y4_PT_LAUNCH(4, launch_stage<kStDirectStep>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
 		}
+		Y4Ray *const ray_buf[2] = {pt->wave.ray, pt->wave.ray_next};
 		for(int sub = 0; sub < sc.n_paths; ++sub)
 		{
 			int cur = 0;
 			uint32_t *n_cur = new_queue_count(0);
+			W.ray = ray_buf[0]; W.ray_next = ray_buf[0];
 			Q.in_q = pt->q_hit0; Q.in_count = n_hit0; Q.out_q = pt->q_path[cur]; Q.out_count = n_cur; Q.sh_q = pt->q_shadow; Q.sh_count = nullptr;
 			a.all_lights = 1; a.sub = sub; a.l_prev = (sub == 0 && !all_lk.empty()) ? all_lk.back().first : -1; a.k_prev = a.l_prev >= 0 ? all_lk.back().second : -1;
-			Y4_PT_LAUNCH(3, k_pt_stage<kStStart><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
-			for(int depth = 0; depth < sc.bounces; ++depth)
+			Y4_PT_LAUNCH(3, launch_stage<kStStart>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
+			for(int depth = 0; depth <= sc.bounces; ++depth)
 			{
-				Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, pt->q_path[cur], n_cur);
-				Q.in_q = pt->q_path[cur]; Q.in_count = n_cur; Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(sc.n_lights ? 1 : -1);
-				a.all_lights = 0; a.depth = depth; a.sub = sub;
-				Y4_PT_LAUNCH(3, k_pt_stage<kStVertex><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
+				const bool closing = depth == sc.bounces;
+				if(closing && !sc.n_lights) break;                       // nothing waits to be folded in
+				W.ray = ray_buf[depth & 1]; W.ray_next = ray_buf[(depth + 1) & 1];
+				if(!closing) Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, pt->q_path[cur], n_cur);
+				uint32_t *n_next = new_queue_count(depth + 1 < sc.bounces ? 0 : -1);
+				Q.in_q = pt->q_path[cur]; Q.in_count = n_cur; Q.out_q = pt->q_path[cur ^ 1]; Q.out_count = n_next;
+				Q.sh_q = pt->q_shadow; Q.sh_count = new_queue_count(sc.n_lights && !closing ? 1 : -1);
+				a.all_lights = 0; a.depth = depth; a.sub = sub; a.l_prev = -1; a.k_prev = sc.n_lights ? max_ls - 1 : -1;
+				Y4_PT_LAUNCH(3, launch_stage<kStPath>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
+				if(closing) break;
 				if(sc.n_lights)
 				{
 					Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
 					for(int k = 1; k < max_ls; ++k)
 					{
-						Q.sh_count = new_queue_count(1);
+						Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
 						a.l_prev = -1; a.k_prev = k - 1; a.l = -1; a.k = k;
-						Y4_PT_LAUNCH(4, k_pt_stage<kStDirectStep><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
+						Y4_PT_LAUNCH(4, launch_stage<kStDirectStep>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
 						Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
 					}
 				}
-				uint32_t *n_next = new_queue_count(depth + 1 < sc.bounces ? 0 : -1);
-				Q.out_q = pt->q_path[cur ^ 1]; Q.out_count = n_next; Q.sh_count = nullptr;
-				a.k_prev = sc.n_lights ? max_ls - 1 : -1;
-				Y4_PT_LAUNCH(4, k_pt_stage<kStExtend><<<grid, kPtThreads, 0, st>>>(dsc, W, ps, a, Q));
 				cur ^= 1; n_cur = n_next;
 			}
 		}
+		W.ray = ray_buf[0]; W.ray_next = ray_buf[1];
 		Y4_PT_LAUNCH(5, k_pt_splat<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, pt->d_film_w, pt->d_film_rgba));
 		Y4_CUDA(ctx, cudaGetLastError());
 	}

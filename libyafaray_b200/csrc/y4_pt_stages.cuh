@@ -18,12 +18,15 @@ struct Y4PtWave
 	uint32_t *lnum;        // light chosen by estimateOneDirectLight for the current vertex
 	float *col;            // [n*4] radiance of the pixel-sample (rgb) + alpha
 	float *pcol;           // [n*4] path_col (sum over the path_samples sub-paths)
-	float *thr;            // [n*4] throughput
+	float *thr;            // [n*4] throughput arriving at the current vertex
+	float *pthr;           // [n*4] throughput at the previous vertex after Russian roulette (its light estimate is folded in one stage later)
 	float *lcol;           // [n*4] emitted light picked up at the current vertex
 	float *acc_a, *acc_b;  // [n*4] per-light sums of the light-sample / BSDF-sample estimators
 	float *lsamp;          // [n*4] last light sample drawn for this pixel-sample: s1, s2, light, k (the reference draws
 	                       //       the same numbers at every vertex of a pixel-sample, see y4_light_sample_numbers)
-	Y4Ray *ray; Y4Hit *hit; Y4Hit *hit0;
+	Y4Ray *ray;            // ray that produced the current vertex
+	Y4Ray *ray_next;       // ray leaving the current vertex (the host alternates the two buffers per bounce)
+	Y4Hit *hit; Y4Hit *hit0;
 	Y4Ray *sray;           // [2n] shadow rays: slot 0 at [i], slot 1 at [n + i]
 	Y4Hit *shit;           // [2n]
 	float *scontrib;       // [2n*4]
@@ -168,7 +171,7 @@ Y4_HD int y4_light_num_samples(const Y4PtScene &sc, const Y4PtLight &L)
 // does this path take sample k of a light now?  (shared by the sample and the resolve step)
 Y4_HD bool y4_direct_active(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t f, bool all_lights, int light, int k, int &l, int &num_samples)
 {
-	if(!(f & Y4_PF_DIRECT) || (!all_lights && !(f & Y4_PF_ALIVE))) return false;
+	if(!(f & Y4_PF_DIRECT)) return false;          // set by the camera-hit / path-vertex step, cleared when the estimate is folded in
 	l = all_lights ? light : (sc.n_lights > 1 ? (int) W.lnum[i] : 0);
 	num_samples = y4_light_num_samples(sc, sc.lights[l]);
 	return k < num_samples;
@@ -219,6 +222,7 @@ Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 }
 
 // ---- step: fold the shadow-ray results of sample k into the light's estimators ---------------------
+// (one-light estimates multiply by the throughput stored at the vertex they belong to: W.pthr)
 Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t &f, bool all_lights, int light, int k)
 {
 	const uint32_t n = W.n;
@@ -228,7 +232,7 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 	const float4 c0 = ld4(W.scontrib, i), c1 = ld4(W.scontrib, n + i);
 	const int32_t p0 = (f & Y4_PF_S0) ? W.shit[i].prim : -1, p1 = (f & Y4_PF_S1) ? W.shit[n + i].prim : -1;
 	const float4 base = all_lights ? ld4(W.col, i) : ld4(W.pcol, i);
-	const float4 thr4 = all_lights ? f4(0.f, 0.f, 0.f, 0.f) : ld4(W.thr, i);
+	const float4 thr4 = all_lights ? f4(0.f, 0.f, 0.f, 0.f) : ld4(W.pthr, i);
 	const float4 lc4 = all_lights ? f4(0.f, 0.f, 0.f, 0.f) : ld4(W.lcol, i);
 	const Y4PtLight &L = sc.lights[l];
 	// running sums over the light's samples live in acc_a/acc_b only between samples (k > 0)
@@ -262,26 +266,14 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 	}
 }
 
-// ---- step: BSDF sample that extends sub-path `sub` at bounce `depth` (integrate(), :163-231) --------
-// FIRST: depth == 0 (the vertex is the camera hit).  Returns true when W.ray[i] holds the next ray of the path.
+// ---- step: BSDF sample that extends sub-path `sub` from vertex `vx` (integrate(), :163-231) ---------
+// FIRST: the vertex is the camera hit (bounce 0), else the vertex reached by bounce `depth - 1`.
+// thr: throughput at the vertex in, throughput along the new ray out.  Returns true when `out` is the next ray.
 template<bool FIRST>
-Y4_HD bool y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, int depth, int sub)
+Y4_HD bool y4_bounce_sample(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp, int depth, int sub, const Y4Vertex &vx, C3 &thr, Y4Ray &out)
 {
-	const uint32_t pix = W.pix[i], samp = W.samp[i];
-	const Y4Hit h = FIRST ? ld_hit(W.hit0, i) : ld_hit(W.hit, i);
-	Y4Ray r;
-	float4 thr4 = f4(0.f, 0.f, 0.f, 0.f);
-	if(!FIRST) { r = ld_ray(W.ray, i); thr4 = ld4(W.thr, i); }
-	if(FIRST)
-	{
-		f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIFF1 | Y4_PF_DIRECT);
-		if(!(f & Y4_PF_PATHS)) return false;
-		r = y4_primary_ray(sc, ps, pix, samp);
-	}
-	else if(!(f & Y4_PF_ALIVE)) return false;
 	const Y4PixelId s = y4_pixel_id(sc, ps, pix, samp);
 	const uint32_t offs = (uint32_t) sc.n_paths * s.sample + s.offset + (uint32_t) sub;
-	const Y4Vertex vx = y4_vertex(sc, r, h);
 	float s1, s2; uint32_t sflags;
 	if(FIRST)
 	{
@@ -299,32 +291,26 @@ Y4_HD bool y4_pt_bounce_sample(const Y4PtScene &sc, const Y4PtWave &W, const Y4P
 	float w = 0.f, pdf; bool sampled;
 	C3 scol = y4_mat_sample(vx.m, vx.sp, vx.wo, s1, s2, sflags, wi, w, pdf, sampled);
 	scol = cscale(scol, w);
-	if(FIRST) st3(W.thr, i, scol);
+	if(FIRST) thr = scol;
 	else
 	{
-		if(cblack(scol)) { f &= ~(uint32_t) Y4_PF_ALIVE; return false; }
-		st3(W.thr, i, cmul(c3(thr4.x, thr4.y, thr4.z), scol));
+		if(cblack(scol)) return false;
+		thr = cmul(thr, scol);
 	}
-	if(!sampled) { f &= ~(uint32_t) Y4_PF_ALIVE; return false; }   // reference: direction undefined
-	st_ray(W.ray, i, y4_mk_ray(vx.sp.p, sc.ray_min_dist, wi, -1.f));
-	f |= Y4_PF_ALIVE;
+	if(!sampled) return false;                                 // reference: direction undefined
+	out = y4_mk_ray(vx.sp.p, sc.ray_min_dist, wi, -1.f);
 	return true;
 }
 
 // ---- step: the extended ray's hit (integrate(), :191-207 and :232-266) ------------------------------
-// returns true (and fills vx) when the vertex wants a one-light estimate (Y4_PF_DIRECT set, W.lnum chosen)
-Y4_HD bool y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, int depth, int sub, Y4Vertex &vx)
+// Pure logic on loaded state.  Returns 0: the path ended (background or Russian roulette); 1: the vertex needs no
+// light estimate (its emission, if any, goes into `add` = lcol * throughput); 2: one-light estimate wanted
+// (`emit` = lcol so far, light index chosen into W.lnum when there is more than one).
+Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t pix, uint32_t samp, uint32_t &f, int depth, int sub,
+                        const Y4Vertex &vx, C3 &thr, C3 &emit)
 {
-	const Y4Hit h = ld_hit(W.hit, i);
-	const Y4Ray r = ld_ray(W.ray, i);
-	const float4 thr4 = ld4(W.thr, i);
-	const uint32_t pix = W.pix[i], samp = W.samp[i];
-	if(!(f & Y4_PF_ALIVE)) return false;
-	if(h.prim < 0) { f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return false; }     // hit background: continue / break
-	vx = y4_vertex(sc, r, h);
 	const Y4PtMaterial &m = vx.m;
-	C3 thr = c3(thr4.x, thr4.y, thr4.z);
-	C3 emit = c3f(0.f);
+	emit = c3f(0.f);
 	bool direct;
 	if(depth == 0)
 	{
@@ -341,32 +327,22 @@ Y4_HD bool y4_pt_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 			const Y4PixelId s = y4_pixel_id(sc, ps, pix, samp);
 			const float random_value = y4_hash_uniform(sc.rr_seed ^ s.offset, s.sample, (uint32_t) (sub * 64 + depth));
 			const float probability = cmax(thr);
-			if(probability <= 0.f || probability < random_value) { f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return false; }
+			if(probability <= 0.f || probability < random_value) return 0;
 			thr = cscale(thr, xdiv(1.f, probability));
-			st3(W.thr, i, thr);
 		}
 	}
 	if(sc.n_lights == 0) direct = false;
-	if(direct)
+	if(!direct) return 1;
+	// light choice of estimateOneDirectLight: Halton(2) at base offset + a per-call counter.  The
+	// reference counter is per CPU thread (call-order dependent); here it is a per-vertex index.
+	// With one light every draw picks light 0 (min(int(h * 1), 0)): nothing to compute or store.
+	if(sc.n_lights > 1)
 	{
-		// light choice of estimateOneDirectLight: Halton(2) at base offset + a per-call counter.  The
-		// reference counter is per CPU thread (call-order dependent); here it is a per-vertex index.
-		// With one light every draw picks light 0 (min(int(h * 1), 0)): nothing to compute or store.
-		if(sc.n_lights > 1)
-		{
-			const uint32_t corr = (pix * 1009u + ps.pass_offs + samp) * (uint32_t) (sc.bounces * sc.n_paths) + (uint32_t) (sub * sc.bounces + depth);
-			const int lnum = (int) xmul(y4_halton2_at(sc.base_sampling_offset + corr - 1u, 1u), (float) sc.n_lights);
-			W.lnum[i] = (uint32_t) (lnum < sc.n_lights - 1 ? lnum : sc.n_lights - 1);
-		}
-		st3(W.lcol, i, emit);
-		f |= Y4_PF_DIRECT;
-		return true;
+		const uint32_t corr = (pix * 1009u + ps.pass_offs + samp) * (uint32_t) (sc.bounces * sc.n_paths) + (uint32_t) (sub * sc.bounces + depth);
+		const int lnum = (int) xmul(y4_halton2_at(sc.base_sampling_offset + corr - 1u, 1u), (float) sc.n_lights);
+		W.lnum[i] = (uint32_t) (lnum < sc.n_lights - 1 ? lnum : sc.n_lights - 1);
 	}
-	// lcol = 0 (* num_lights) + emit;  path_col += lcol * throughput
-	const C3 lcol = cadd(c3f(0.f), emit);
-	st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, thr)));
-	f &= ~(uint32_t) Y4_PF_DIRECT;
-	return false;
+	return 2;
 }
 
 // ==== fused wavefront stages ===========================================================================
@@ -407,37 +383,80 @@ Y4_HD uint32_t y4_stage_direct_step(const Y4PtScene &sc, const Y4PtWave &W, cons
 	return push;
 }
 
-// start sub-path `sub` at the camera hit: [resolve the last all-lights sample] + BSDF sample at depth 0
+// start sub-path `sub` at the camera hit: [resolve the last all-lights sample] + BSDF sample of bounce 0 -> W.ray_next
 Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l_last, int k_last, int sub)
 {
 	uint32_t f = W.flags[i];
+	const uint32_t pix = W.pix[i], samp = W.samp[i];
+	const Y4Hit h = ld_hit(W.hit0, i);
 	if(l_last >= 0) y4_pt_direct_resolve(sc, W, i, f, true, l_last, k_last);
-	const bool go = y4_pt_bounce_sample<true>(sc, W, ps, i, f, 0, sub);
+	f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIFF1 | Y4_PF_DIRECT);
+	bool go = false;
+	if(f & Y4_PF_PATHS)
+	{
+		const Y4Vertex vx = y4_vertex(sc, y4_primary_ray(sc, ps, pix, samp), h);
+		C3 thr = c3f(0.f); Y4Ray out;
+		go = y4_bounce_sample<true>(sc, ps, pix, samp, 0, sub, vx, thr, out);
+		st3(W.thr, i, thr);
+		if(go) { st_ray(W.ray_next, i, out); f |= Y4_PF_ALIVE; }
+	}
 	W.flags[i] = f;
 	return go ? (uint32_t) Y4_PUSH_PATH : 0u;
 }
 
-// path vertex: hit processing (emission, Russian roulette, light choice) + first sample of the chosen light.
-Y4_HD uint32_t y4_stage_vertex(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub)
+// One bounce of the path loop in a single stage over the paths whose ray W.ray was just traced:
+//   1. fold in the one-light estimate of the previous vertex (its shadow rays were traced meanwhile);
+//   2. this vertex: emission, Russian roulette, light choice, first light sample -> shadow rays;
+//   3. BSDF sample -> the next ray in W.ray_next.
+// A path stays on the output queue while it has a ray to trace OR an estimate waiting to be folded in (such a
+// finished path gets an empty ray).  depth == sc.bounces is the closing call: step 1 only.
+Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub, int k_last)
 {
 	uint32_t f = W.flags[i];
-	const float4 cache = ld4(W.lsamp, i);
-	Y4Vertex vx;
+	const bool closing = depth >= sc.bounces;
+	// state of this vertex, requested before anything depends on it
+	float4 cache = f4(0.f, 0.f, 0.f, 0.f), thr4 = cache;
+	Y4Hit h; h.t = 0.f; h.bu = 0.f; h.bv = 0.f; h.prim = -1;
+	Y4Ray r = y4_null_ray();
+	uint32_t pix = 0u, samp = 0u;
+	if(!closing)
+	{
+		cache = ld4(W.lsamp, i); thr4 = ld4(W.thr, i); h = ld_hit(W.hit, i); r = ld_ray(W.ray, i); pix = W.pix[i]; samp = W.samp[i];
+	}
+	if(depth > 0 && k_last >= 0) y4_pt_direct_resolve(sc, W, i, f, false, -1, k_last);
 	uint32_t push = 0u;
-	if(y4_pt_bounce_hit(sc, W, ps, i, f, depth, sub, vx)) push = y4_pt_direct(sc, W, ps, i, f, false, -1, 0, vx, cache);
+	if(closing || !(f & Y4_PF_ALIVE)) { f &= ~(uint32_t) Y4_PF_ALIVE; W.flags[i] = f; return 0u; }
+	if(h.prim < 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return 0u; }     // hit background: continue / break
+	const Y4Vertex vx = y4_vertex(sc, r, h);
+	C3 thr = c3(thr4.x, thr4.y, thr4.z), emit;
+	const int what = y4_bounce_hit(sc, W, ps, i, pix, samp, f, depth, sub, vx, thr, emit);
+	if(what == 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return 0u; }
+	if(what == 2)
+	{
+		st3(W.lcol, i, emit);
+		st3(W.pthr, i, thr);
+		f |= Y4_PF_DIRECT;
+		push |= y4_pt_direct(sc, W, ps, i, f, false, -1, 0, vx, cache);
+	}
+	else
+	{
+		// lcol = 0 (* num_lights) + emit;  path_col += lcol * throughput
+		const C3 lcol = cadd(c3f(0.f), emit);
+		st3(W.pcol, i, cadd(ld3(W.pcol, i), cmul(lcol, thr)));
+		f &= ~(uint32_t) Y4_PF_DIRECT;
+	}
+	bool go = false;
+	if(depth + 1 < sc.bounces)
+	{
+		Y4Ray out;
+		go = y4_bounce_sample<false>(sc, ps, pix, samp, depth + 1, sub, vx, thr, out);
+		if(go) { st_ray(W.ray_next, i, out); st3(W.thr, i, thr); }
+		else if(f & Y4_PF_DIRECT) st_ray(W.ray_next, i, y4_null_ray());
+	}
+	if(!go) f &= ~(uint32_t) Y4_PF_ALIVE;
+	if(go || (f & Y4_PF_DIRECT)) push |= Y4_PUSH_PATH;
 	W.flags[i] = f;
 	return push;
-}
-
-// close the vertex: [resolve the last light sample] + BSDF sample for the next bounce
-Y4_HD uint32_t y4_stage_extend(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub, int k_last)
-{
-	uint32_t f = W.flags[i];
-	if(k_last >= 0) y4_pt_direct_resolve(sc, W, i, f, false, -1, k_last);
-	bool go = false;
-	if(depth + 1 < sc.bounces) go = y4_pt_bounce_sample<false>(sc, W, ps, i, f, depth + 1, sub);
-	W.flags[i] = f;
-	return go ? (uint32_t) Y4_PUSH_PATH : 0u;
 }
 
 // ---- stage: close the pixel-sample and splat it into the film ----------------------------------------

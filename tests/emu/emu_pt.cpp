@@ -76,13 +76,13 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	const uint32_t n = (uint32_t) sc.width * sc.height * ns_local;
 	if(n == 0) return 0;
 	std::vector<uint32_t> pix(n), samp(n), fl(n), lnum(n);
-	std::vector<float4> col(n), pcol(n), thr(n), lcol(n), acc_a(n), acc_b(n), lsamp(n), scontrib(2ull * n);
-	std::vector<Y4Ray> ray(n), sray(2ull * n);
+	std::vector<float4> col(n), pcol(n), thr(n), pthr(n), lcol(n), acc_a(n), acc_b(n), lsamp(n), scontrib(2ull * n);
+	std::vector<Y4Ray> ray(n), ray2(n), sray(2ull * n);
 	std::vector<Y4Hit> hit(n), hit0(n), shit(2ull * n);
 	Y4PtWave W;
 	W.n = n; W.pix = pix.data(); W.samp = samp.data(); W.flags = fl.data(); W.lnum = lnum.data();
-	W.col = &col[0].x; W.pcol = &pcol[0].x; W.thr = &thr[0].x; W.lcol = &lcol[0].x; W.acc_a = &acc_a[0].x; W.acc_b = &acc_b[0].x; W.lsamp = &lsamp[0].x;
-	W.ray = ray.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = &scontrib[0].x;
+	W.col = &col[0].x; W.pcol = &pcol[0].x; W.thr = &thr[0].x; W.lcol = &lcol[0].x; W.acc_a = &acc_a[0].x; W.acc_b = &acc_b[0].x; W.lsamp = &lsamp[0].x; W.pthr = &pthr[0].x;
+	W.ray = ray.data(); W.ray_next = ray2.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = &scontrib[0].x;
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
 	for(uint32_t i = 0; i < n; ++i) { pix[i] = i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
 	// same stage sequence as y4gpu_pt_render_pass (y4_pt.cu), queues as vectors
@@ -100,16 +100,22 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		q_shadow.clear();
 		for(uint32_t i : q_hit0) push(y4_stage_direct_step(sc, W, ps, i, true, all_lk[j].first, all_lk[j].second, all_lk[j + 1].first, all_lk[j + 1].second), i, n, nullptr, &q_shadow);
 	}
+	Y4Ray *const ray_buf[2] = {ray.data(), ray2.data()};
 	for(int sub = 0; sub < sc.n_paths; ++sub)
 	{
 		q_cur.clear();
 		const bool res = sub == 0 && !all_lk.empty();
+		W.ray = ray_buf[0]; W.ray_next = ray_buf[0];
 		for(uint32_t i : q_hit0) push(y4_stage_start(sc, W, ps, i, res ? all_lk.back().first : -1, res ? all_lk.back().second : -1, sub), i, n, &q_cur, nullptr);
-		for(int depth = 0; depth < sc.bounces; ++depth)
+		for(int depth = 0; depth <= sc.bounces; ++depth)
 		{
-			trace(bvh, Y4_TRACE_CLOSEST, W.ray, q_cur.data(), q_cur.size(), W.hit);
-			q_shadow.clear();
-			for(uint32_t i : q_cur) push(y4_stage_vertex(sc, W, ps, i, depth, sub), i, n, nullptr, &q_shadow);
+			const bool closing = depth == sc.bounces;
+			if(closing && !sc.n_lights) break;
+			W.ray = ray_buf[depth & 1]; W.ray_next = ray_buf[(depth + 1) & 1];
+			if(!closing) trace(bvh, Y4_TRACE_CLOSEST, W.ray, q_cur.data(), q_cur.size(), W.hit);
+			q_shadow.clear(); q_next.clear();
+			for(uint32_t i : q_cur) push(y4_stage_path(sc, W, ps, i, depth, sub, sc.n_lights ? max_ls - 1 : -1), i, n, &q_next, &q_shadow);
+			if(closing) break;
 			if(sc.n_lights)
 			{
 				trace(bvh, Y4_TRACE_SHADOW, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
@@ -120,11 +126,10 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 					trace(bvh, Y4_TRACE_SHADOW, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
 				}
 			}
-			q_next.clear();
-			for(uint32_t i : q_cur) push(y4_stage_extend(sc, W, ps, i, depth, sub, sc.n_lights ? max_ls - 1 : -1), i, n, &q_next, nullptr);
 			q_cur.swap(q_next);
 		}
 	}
+	W.ray = ray_buf[0];
 	for(uint32_t i = 0; i < n; ++i) y4_pt_finish_splat(sc, W, ps, i, film_w, film_rgba);
 	return 0;
 }
