@@ -6,6 +6,8 @@
 #include <cstring>
 #include <vector>
 
+constexpr int kMaxLanes = 4;
+
 struct Y4Pt
 {
 	Y4PtScene h_scene;                 // passed to every kernel by value (device pointers inside)
@@ -22,11 +24,19 @@ struct Y4Pt
 	// film
 	float *d_film_w = nullptr, *d_film_rgba = nullptr;      // in use
 	float *own_film_w = nullptr, *own_film_rgba = nullptr;  // owned (when the caller gave none)
-	// wave state
-	uint32_t cap = 0;
-	Y4PtWave wave = {};
-	void *wave_mem = nullptr;
-	uint32_t *q_hit0 = nullptr, *q_path[2] = {nullptr, nullptr}, *q_shadow = nullptr;   // index queues (in wave_mem)
+	// wave state: several wavefronts in flight on separate streams ("lanes"), so that the issue-bound traversal of one
+	// shares the SMs with the latency-bound shading of the other
+	struct Lane
+	{
+		uint32_t cap = 0;
+		Y4PtWave wave = {};
+		void *mem = nullptr;
+		uint32_t *q_hit0 = nullptr, *q_path[2] = {nullptr, nullptr}, *q_shadow = nullptr;   // index queues (in mem)
+		cudaStream_t stream = nullptr;      // lane 0: the context's stream; lane 1: own stream, forked/joined per pass
+		cudaEvent_t done = nullptr;
+	} lanes[kMaxLanes];
+	int n_lanes = 2, trace_blocks_shared = 2;
+	cudaEvent_t ev_fork = nullptr;
 	// per-launch counters: 64-bit slots, zeroed once per pass; a queue length is the low word of its slot
 	unsigned long long *d_counters = nullptr, *h_counters = nullptr; size_t counters_cap = 0;
 	std::vector<std::pair<uint32_t, int>> counter_kinds;      // (slot, 0 closest queue / 1 shadow queue) of the last pass
@@ -139,30 +149,30 @@ inline int pt_grid(const y4gpu_ctx *ctx, uint32_t n)
 	return (int) (want < full ? (want ? want : 1u) : full);
 }
 
-void pt_free_wave(Y4Pt *pt)
+void pt_free_wave(Y4Pt::Lane &L)
 {
-	cudaFree(pt->wave_mem); pt->wave_mem = nullptr; pt->cap = 0;
+	cudaFree(L.mem); L.mem = nullptr; L.cap = 0;
 }
 
 // One allocation carved into the SoA arrays of the wave (all 16-byte aligned).
-int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt *pt, uint32_t cap)
+int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt::Lane &L, uint32_t cap)
 {
-	if(cap <= pt->cap) return Y4GPU_OK;
-	pt_free_wave(pt);
+	if(cap <= L.cap) return Y4GPU_OK;
+	pt_free_wave(L);
 	const size_t n = cap;
 	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 16 /*pthr*/ + 2 * 32 + 16 + 16 /*ray x2 hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/
 	                          + 16 /*lsamp*/ + 5 * 4 /*queues*/) + 512;
-	Y4_CUDA(ctx, cudaMalloc(&pt->wave_mem, bytes));
-	char *p = (char *) pt->wave_mem;
+	Y4_CUDA(ctx, cudaMalloc(&L.mem, bytes));
+	char *p = (char *) L.mem;
 	auto take = [&](size_t b) { char *r = p; p += (b + 15) & ~(size_t) 15; return (void *) r; };
-	Y4PtWave &W = pt->wave;
+	Y4PtWave &W = L.wave;
 	W.col = (float *) take(n * 16); W.pcol = (float *) take(n * 16); W.thr = (float *) take(n * 16); W.lcol = (float *) take(n * 16);
 	W.acc_a = (float *) take(n * 16); W.acc_b = (float *) take(n * 16); W.lsamp = (float *) take(n * 16);
 	W.ray = (Y4Ray *) take(n * 32); W.ray_next = (Y4Ray *) take(n * 32); W.pthr = (float *) take(n * 16); W.hit = (Y4Hit *) take(n * 16); W.hit0 = (Y4Hit *) take(n * 16);
 	W.sray = (Y4Ray *) take(2 * n * 32); W.shit = (Y4Hit *) take(2 * n * 16); W.scontrib = (float *) take(2 * n * 16);
 	W.pix = (uint32_t *) take(n * 4); W.samp = (uint32_t *) take(n * 4); W.flags = (uint32_t *) take(n * 4); W.lnum = (uint32_t *) take(n * 4);
-	pt->q_hit0 = (uint32_t *) take(n * 4); pt->q_path[0] = (uint32_t *) take(n * 4); pt->q_path[1] = (uint32_t *) take(n * 4); pt->q_shadow = (uint32_t *) take(2 * n * 4);
-	pt->cap = cap;
+	L.q_hit0 = (uint32_t *) take(n * 4); L.q_path[0] = (uint32_t *) take(n * 4); L.q_path[1] = (uint32_t *) take(n * 4); L.q_shadow = (uint32_t *) take(2 * n * 4);
+	L.cap = cap;
 	return Y4GPU_OK;
 }
 
@@ -181,7 +191,13 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 {
 	Y4Pt *pt = ctx->pt;
 	if(!pt) return;
-	pt_free_wave(pt);
+	for(Y4Pt::Lane &L : pt->lanes)
+	{
+		pt_free_wave(L);
+		if(L.done) cudaEventDestroy(L.done);
+	}
+	for(int l = 1; l < kMaxLanes; ++l) if(pt->lanes[l].stream) cudaStreamDestroy(pt->lanes[l].stream);
+	if(pt->ev_fork) cudaEventDestroy(pt->ev_fork);
 	cudaFree(pt->d_lights); cudaFree(pt->d_mats); cudaFree(pt->d_normals); cudaFree(pt->d_tri_shade);
 	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime); cudaFree(pt->d_sigma_d); cudaFree(pt->d_magic);
 	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); cudaFree(pt->d_pixel_list);
@@ -212,6 +228,8 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	if(!ctx->pt) ctx->pt = new Y4Pt;
 	if(const char *e = getenv("Y4GPU_PT_MIN_BLOCKS")) ctx->pt->stage_min_blocks = atoi(e);
+	if(const char *e = getenv("Y4GPU_PT_LANES")) ctx->pt->n_lanes = atoi(e) < 1 ? 1 : (atoi(e) > kMaxLanes ? kMaxLanes : atoi(e));
+	if(const char *e = getenv("Y4GPU_PT_TRACE_BLOCKS")) ctx->pt->trace_blocks_shared = atoi(e);
 	Y4Pt *pt = ctx->pt;
 	if(!pt->ev0) { Y4_CUDA(ctx, cudaEventCreate(&pt->ev0)); Y4_CUDA(ctx, cudaEventCreate(&pt->ev1)); }
 	cudaStream_t st = ctx->stream;
@@ -405,7 +423,20 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	}
 	uint32_t wave_size = pt->params.wave_size ? pt->params.wave_size : (1u << 22);
 	if(total < wave_size) wave_size = (uint32_t) (total ? total : 1);
-	{ const int rc = pt_alloc_wave(ctx, pt, wave_size); if(rc) return rc; }
+	const bool prof = pt->params.profile != 0;
+	// lanes: consecutive waves alternate between two streams (profile mode times kernels one by one: single lane)
+	const uint64_t n_waves_total = total ? (total + wave_size - 1) / wave_size : 0;
+	const int n_lanes = (pt->n_lanes > 1 && !prof && n_waves_total > 1) ? (int) (n_waves_total < (uint64_t) pt->n_lanes ? n_waves_total : (uint64_t) pt->n_lanes) : 1;
+	pt->lanes[0].stream = st;
+	if(n_lanes > 1 && !pt->ev_fork) Y4_CUDA(ctx, cudaEventCreateWithFlags(&pt->ev_fork, cudaEventDisableTiming));
+	for(int l = 1; l < n_lanes; ++l)
+	{
+		if(!pt->lanes[l].stream) Y4_CUDA(ctx, cudaStreamCreateWithFlags(&pt->lanes[l].stream, cudaStreamNonBlocking));
+		if(!pt->lanes[l].done) Y4_CUDA(ctx, cudaEventCreateWithFlags(&pt->lanes[l].done, cudaEventDisableTiming));
+	}
+	for(int l = 0; l < n_lanes; ++l) { const int rc = pt_alloc_wave(ctx, pt->lanes[l], wave_size); if(rc) return rc; }
+	const int trace_blocks = n_lanes > 1 ? pt->trace_blocks_shared : 0;
+	const int stage_minb = n_lanes > 1 && pt->stage_min_blocks < 3 ? 3 : pt->stage_min_blocks;
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass_number;
 	const Y4PtScene &dsc = sc;
 	// the (light, sample) sequence of estimateAllDirectLight at the camera hit
@@ -434,7 +465,6 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		return reinterpret_cast<uint32_t *>(new_slot());
 	};
 	// profile mode: an event after every launch attributes device time to kernel classes; traversal runs counted
-	const bool prof = pt->params.profile != 0;
 	std::vector<int> prof_cls;
 	auto mark = [&](int cls) -> int
 	{
@@ -447,11 +477,20 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	{ const int rc_ = mark(-1); if(rc_) return rc_; }
 #define Y4_PT_LAUNCH(cls, ...) do { __VA_ARGS__; ++own_launches; const int rc_ = mark(cls); if(rc_) return rc_; } while(0)
 #define Y4_PT_TRACE(kind, rays, hits, n_max, queue, count) do { \
-		int rc_ = y4_launch_trace_wave(ctx, kind, prof, rays, hits, n_max, queue, count, new_slot(), pt->d_counters + (kind == Y4_TRACE_CLOSEST ? 0 : 3)); \
+		int rc_ = y4_launch_trace_wave(ctx, kind, prof, rays, hits, n_max, queue, count, new_slot(), pt->d_counters + (kind == Y4_TRACE_CLOSEST ? 0 : 3), st, trace_blocks); \
 		if(rc_ || (rc_ = mark(kind == Y4_TRACE_CLOSEST ? 1 : 2))) return rc_; } while(0)
-	for(uint64_t first = 0; first < total; first += wave_size)
+	if(n_lanes > 1)
 	{
-		Y4PtWave W = pt->wave;
+		// fork: the other lanes start after everything queued so far on the context's stream (scene upload, counter reset)
+		Y4_CUDA(ctx, cudaEventRecord(pt->ev_fork, pt->lanes[0].stream));
+		for(int l = 1; l < n_lanes; ++l) Y4_CUDA(ctx, cudaStreamWaitEvent(pt->lanes[l].stream, pt->ev_fork, 0));
+	}
+	uint64_t wave_index = 0;
+	for(uint64_t first = 0; first < total; first += wave_size, ++wave_index)
+	{
+		Y4Pt::Lane &lane = pt->lanes[wave_index % (uint64_t) n_lanes];
+		st = lane.stream;
+		Y4PtWave W = lane.wave;
 		W.n = (uint32_t) ((total - first) < wave_size ? (total - first) : wave_size);
 		const int grid = pt_grid(ctx, W.n);
 		StageArgs a = {0, -1, -1, -1, -1, 0, 0};
@@ -460,47 +499,47 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, ns_local, shard_index, shard_count));
 		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, nullptr, nullptr); pt->dense_closest += W.n;
 		uint32_t *n_hit0 = new_queue_count(-1);
-		Q.out_q = pt->q_hit0; Q.out_count = n_hit0; Q.sh_q = pt->q_shadow; Q.sh_count = new_queue_count(1);
+		Q.out_q = lane.q_hit0; Q.out_count = n_hit0; Q.sh_q = lane.q_shadow; Q.sh_count = new_queue_count(1);
 		a.l = all_lk.empty() ? -1 : all_lk[0].first;
-		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
+		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
 		for(size_t j = 0; j < all_lk.size(); ++j)
 		{
-			Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
+			Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
 			if(j + 1 == all_lk.size()) break;          // the last sample is resolved by the start stage
-			Q.in_q = pt->q_hit0; Q.in_count = n_hit0; Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
+			Q.in_q = lane.q_hit0; Q.in_count = n_hit0; Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
 			a.all_lights = 1; a.l_prev = all_lk[j].first; a.k_prev = all_lk[j].second; a.l = all_lk[j + 1].first; a.k = all_lk[j + 1].second;
-			Y4_PT_LAUNCH(4, launch_stage<kStDirectStep>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
+			Y4_PT_LAUNCH(4, launch_stage<kStDirectStep>(stage_minb, grid, st, dsc, W, ps, a, Q));
 		}
-		Y4Ray *const ray_buf[2] = {pt->wave.ray, pt->wave.ray_next};
+		Y4Ray *const ray_buf[2] = {lane.wave.ray, lane.wave.ray_next};
 		for(int sub = 0; sub < sc.n_paths; ++sub)
 		{
 			int cur = 0;
 			uint32_t *n_cur = new_queue_count(0);
 			W.ray = ray_buf[0]; W.ray_next = ray_buf[0];
-			Q.in_q = pt->q_hit0; Q.in_count = n_hit0; Q.out_q = pt->q_path[cur]; Q.out_count = n_cur; Q.sh_q = pt->q_shadow; Q.sh_count = nullptr;
+			Q.in_q = lane.q_hit0; Q.in_count = n_hit0; Q.out_q = lane.q_path[cur]; Q.out_count = n_cur; Q.sh_q = lane.q_shadow; Q.sh_count = nullptr;
 			a.all_lights = 1; a.sub = sub; a.l_prev = (sub == 0 && !all_lk.empty()) ? all_lk.back().first : -1; a.k_prev = a.l_prev >= 0 ? all_lk.back().second : -1;
-			Y4_PT_LAUNCH(3, launch_stage<kStStart>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
+			Y4_PT_LAUNCH(3, launch_stage<kStStart>(stage_minb, grid, st, dsc, W, ps, a, Q));
 			for(int depth = 0; depth <= sc.bounces; ++depth)
 			{
 				const bool closing = depth == sc.bounces;
 				if(closing && !sc.n_lights) break;                       // nothing waits to be folded in
 				W.ray = ray_buf[depth & 1]; W.ray_next = ray_buf[(depth + 1) & 1];
-				if(!closing) Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, pt->q_path[cur], n_cur);
+				if(!closing) Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, lane.q_path[cur], n_cur);
 				uint32_t *n_next = new_queue_count(depth + 1 < sc.bounces ? 0 : -1);
-				Q.in_q = pt->q_path[cur]; Q.in_count = n_cur; Q.out_q = pt->q_path[cur ^ 1]; Q.out_count = n_next;
-				Q.sh_q = pt->q_shadow; Q.sh_count = new_queue_count(sc.n_lights && !closing ? 1 : -1);
+				Q.in_q = lane.q_path[cur]; Q.in_count = n_cur; Q.out_q = lane.q_path[cur ^ 1]; Q.out_count = n_next;
+				Q.sh_q = lane.q_shadow; Q.sh_count = new_queue_count(sc.n_lights && !closing ? 1 : -1);
 				a.all_lights = 0; a.depth = depth; a.sub = sub; a.l_prev = -1; a.k_prev = sc.n_lights ? max_ls - 1 : -1;
-				Y4_PT_LAUNCH(3, launch_stage<kStPath>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
+				Y4_PT_LAUNCH(3, launch_stage<kStPath>(stage_minb, grid, st, dsc, W, ps, a, Q));
 				if(closing) break;
 				if(sc.n_lights)
 				{
-					Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
+					Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
 					for(int k = 1; k < max_ls; ++k)
 					{
 						Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
 						a.l_prev = -1; a.k_prev = k - 1; a.l = -1; a.k = k;
-						Y4_PT_LAUNCH(4, launch_stage<kStDirectStep>(pt->stage_min_blocks, grid, st, dsc, W, ps, a, Q));
-						Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, pt->q_shadow, Q.sh_count);
+						Y4_PT_LAUNCH(4, launch_stage<kStDirectStep>(stage_minb, grid, st, dsc, W, ps, a, Q));
+						Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
 					}
 				}
 				cur ^= 1; n_cur = n_next;
@@ -512,6 +551,16 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	}
 #undef Y4_PT_LAUNCH
 #undef Y4_PT_TRACE
+	st = ctx->stream;
+	if(n_lanes > 1)
+	{
+		// join: the context's stream continues after the other lanes
+		for(int l = 1; l < n_lanes; ++l)
+		{
+			Y4_CUDA(ctx, cudaEventRecord(pt->lanes[l].done, pt->lanes[l].stream));
+			Y4_CUDA(ctx, cudaStreamWaitEvent(st, pt->lanes[l].done, 0));
+		}
+	}
 	Y4_CUDA(ctx, cudaMemcpyAsync(pt->h_counters, pt->d_counters, need * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
 	pt->counters_read = false;
 	Y4_CUDA(ctx, cudaEventRecord(pt->ev1, st));

@@ -191,6 +191,8 @@ struct TraceArgs
 	const Y4Ray *rays; uint64_t n; Y4Hit *out;
 	unsigned long long *work_counter, *visit;
 	const uint32_t *queue, *queue_count;
+	cudaStream_t stream;
+	int max_blocks_per_sm;      // 0: as many as fit (persistent grid = one resident wave)
 };
 
 template<int KIND, bool COUNT, int MINB, bool QUEUE>
@@ -204,9 +206,10 @@ int launch_k(y4gpu_ctx *ctx, const TraceArgs &a)
 		if(per_sm < 1) per_sm = 1;
 	}
 	const uint64_t want = (a.n + kTraceThreads - 1) / kTraceThreads;
-	const uint64_t full = (uint64_t) ctx->sm_count * per_sm;     // persistent: one wave of resident CTAs
+	const int use_per_sm = (a.max_blocks_per_sm > 0 && a.max_blocks_per_sm < per_sm) ? a.max_blocks_per_sm : per_sm;
+	const uint64_t full = (uint64_t) ctx->sm_count * use_per_sm;     // persistent: one wave of resident CTAs
 	const int grid = (int) (want < full ? want : full);
-	k_trace<KIND, COUNT, MINB, QUEUE><<<grid, kTraceThreads, 0, ctx->stream>>>(ctx->view(), a.rays, a.n, a.out, a.work_counter, a.visit,
+	k_trace<KIND, COUNT, MINB, QUEUE><<<grid, kTraceThreads, 0, a.stream>>>(ctx->view(), a.rays, a.n, a.out, a.work_counter, a.visit,
 	                                                                          ctx->fetch_threshold, ctx->postpone_div, a.queue, a.queue_count);
 	return Y4GPU_OK;
 }
@@ -227,7 +230,7 @@ int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays,
 	if(counted) Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_visit_counters, 0, 3 * sizeof(unsigned long long), st));
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
 	TraceArgs a; a.rays = d_rays; a.n = n; a.out = d_out; a.work_counter = reinterpret_cast<unsigned long long *>(ctx->d_work_counter);
-	a.visit = ctx->d_visit_counters; a.queue = nullptr; a.queue_count = nullptr;
+	a.visit = ctx->d_visit_counters; a.queue = nullptr; a.queue_count = nullptr; a.stream = st; a.max_blocks_per_sm = 0;
 	int rc;
 	if(kind == Y4_TRACE_CLOSEST) rc = launch<Y4_TRACE_CLOSEST, false>(ctx, counted, a);
 	else if(kind == Y4_TRACE_SHADOW) rc = launch<Y4_TRACE_SHADOW, false>(ctx, counted, a);
@@ -244,10 +247,12 @@ int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays,
 // index queue of at most n_max entries whose length is *queue_count.  work_counter must be zero (the
 // caller hands out a fresh pre-zeroed slot per launch); visit (3 counters) is accumulated when counted.
 int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays, Y4Hit *d_out, uint64_t n_max,
-                         const uint32_t *d_queue, const uint32_t *d_queue_count, unsigned long long *d_work_counter, unsigned long long *d_visit)
+                         const uint32_t *d_queue, const uint32_t *d_queue_count, unsigned long long *d_work_counter, unsigned long long *d_visit,
+                         cudaStream_t stream, int max_blocks_per_sm)
 {
 	if(n_max == 0) return Y4GPU_OK;
 	TraceArgs a; a.rays = d_rays; a.n = n_max; a.out = d_out; a.work_counter = d_work_counter; a.visit = d_visit; a.queue = d_queue; a.queue_count = d_queue_count;
+	a.stream = stream; a.max_blocks_per_sm = max_blocks_per_sm;
 	int rc;
 	if(kind == Y4_TRACE_CLOSEST) rc = d_queue ? launch<Y4_TRACE_CLOSEST, true>(ctx, counted, a) : launch<Y4_TRACE_CLOSEST, false>(ctx, counted, a);
 	else if(kind == Y4_TRACE_SHADOW) rc = d_queue ? launch<Y4_TRACE_SHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_SHADOW, false>(ctx, counted, a);
