@@ -67,7 +67,7 @@ def pt_config_dict(args):
         "width": args.pt_width, "height": args.pt_height, "spp_per_step_per_gpu": args.pt_spp, "bounces": args.pt_bounces,
         "path_samples": 1, "russian_roulette": "off (min_bounces = bounces: the reference's deterministic mode)",
         "samples_per_step_per_gpu": args.pt_width * args.pt_height * args.pt_spp,
-        "l2": "no flush needed: each wavefront streams > 500 MB of path state / rays / hits per bounce (> 126 MB L2)",
+        "l2": "no flush needed: the path state of the wavefronts in flight (2 x 4 Mi paths x 380 B = 3 GB) is far larger than the 126 MB L2",
         "sharding": "AA-pass samples s mod N per GPU, scene + BVH replicated, one NCCL all-reduce of the pass film (5 floats/pixel) per step",
         "secondary": "`raybatch`: C3 (configs[2]) 1M-triangle sphere, 3 x 16 Mi ray batches per GPU per step",
     }
@@ -486,9 +486,20 @@ def run_reference_arm(args):
     print_json(line)
 
 
-# algorithmic bytes per pixel-sample moved by the shading stages: SoA state read + written
-SHADE_BYTES = {"gen": 8 + 32 + 4, "primary": 32 + 16 + 16 + 5 * 16 + 4, "bounce_sample": 100 + 52, "bounce_hit": 76 + 40,
-               "direct": 64 + 96, "resolve": 168 + 68, "splat": 44 + 5 * 4 * 2}
+# Algorithmic bytes moved by the shading stages: SoA path state read + written, 16-byte fields.
+SHADE_BYTES = {
+    # per pixel-sample: pix/samp written, camera ray written
+    "gen": 8 + 32,
+    # per pixel-sample: hit + ray + pix/samp read; col written; for camera hits also hit0, pcol, lsamp, flags, scontrib x2, 1 shadow ray, 2 queue entries
+    "primary_miss": 16 + 32 + 8 + 16 + 4, "primary_hit": 16 + 32 + 8 + 16 + 16 + 16 + 16 + 4 + 32 + 32 + 8,
+    # per camera hit: queue entry, flags, pix/samp, hit0, shadow hits, scontrib x2, col read; col, thr, flags, next ray, queue entry written
+    "start": 4 + 4 + 8 + 16 + 8 + 32 + 16 + 16 + 16 + 4 + 32 + 4,
+    # per path-stage entry: queue entry, flags, hit, ray, thr, pix/samp, lsamp + previous estimate (shadow hits, scontrib x2, lcol, pthr, pcol) read;
+    # flags, pthr, thr, lcol, scontrib x2, 1 shadow ray, next ray, pcol, 2 queue entries written
+    "path": (4 + 4 + 16 + 32 + 16 + 8 + 16) + (8 + 32 + 16 + 16 + 16) + (4 + 16 + 16 + 16 + 32 + 32 + 32 + 16 + 8),
+    # per pixel-sample: col, pcol, flags, pix/samp read; 5 float atomics to the film (box filter: one pixel)
+    "splat": 16 + 16 + 4 + 8 + 5 * 4 * 2,
+}
 
 
 def pt_arm(args, env):
@@ -582,17 +593,16 @@ def pt_arm(args, env):
     n = W * H * spp                                           # pixel-samples per GPU per step
     value = n * world * args.steps / (total_ms * 1e-3) * 1e-6
     peak, peak_src = load_peaks()
-    names = ["fill+camera", "trace_closest", "trace_shadow", "hit+bounce shading", "light sampling+resolve", "splat"]
+    names = ["camera rays", "trace_closest", "trace_shadow", "path stages (camera hit, start, per-bounce)", "extra light-sample stages", "splat"]
     cms = prof["class_ms"][:6]
     dom = int(np.argmax(cms))
-    live = {1: prof["live_closest"], 2: prof["live_shadow"]}
-    n_lights_rounds = 1 + bounces                             # one light, one sample: direct+resolve rounds per pixel-sample
+    hits0 = prof["camera_hits"]
     alg_bytes = {
         0: n * SHADE_BYTES["gen"],
-        1: prof["rays_closest"] * 48 + prof["nodes_closest"] * 80 + prof["tris_closest"] * 48,
-        2: prof["rays_shadow"] * 48 + prof["nodes_shadow"] * 80 + prof["tris_shadow"] * 48,
-        3: n * (SHADE_BYTES["primary"] + bounces * (SHADE_BYTES["bounce_sample"] + SHADE_BYTES["bounce_hit"])),
-        4: n * n_lights_rounds * (SHADE_BYTES["direct"] + SHADE_BYTES["resolve"]),
+        1: prof["rays_closest"] * 48 + (prof["rays_closest"] - n) * 4 + prof["nodes_closest"] * 80 + prof["tris_closest"] * 48,
+        2: prof["rays_shadow"] * 52 + prof["nodes_shadow"] * 80 + prof["tris_shadow"] * 48,
+        3: (n - hits0) * SHADE_BYTES["primary_miss"] + hits0 * (SHADE_BYTES["primary_hit"] + SHADE_BYTES["start"]) + prof["path_entries"] * SHADE_BYTES["path"],
+        4: 0,
         5: n * SHADE_BYTES["splat"],
     }
     achieved = alg_bytes[dom] / (cms[dom] * 1e-3) * 1e-9 if cms[dom] > 0 else 0.0
@@ -600,9 +610,8 @@ def pt_arm(args, env):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": pt_config_dict(args),
-        "rays_per_sample": {"closest": st["rays_closest"] / st["samples"], "shadow_slots": st["rays_shadow"] / st["samples"],
-                            "live_closest": prof["live_closest"] / prof["samples"], "live_shadow": prof["live_shadow"] / prof["samples"]},
-        "mrays_s_live": (prof["live_closest"] + prof["live_shadow"]) / prof["samples"] * value,
+        "rays_per_sample": {"closest": st["rays_closest"] / st["samples"], "shadow": st["rays_shadow"] / st["samples"]},
+        "mrays_s": (st["rays_closest"] + st["rays_shadow"]) / st["samples"] * value,
         "film_check": {"weight_sum": wsum, "mean_rgb": mean_rgb},
         "gpu_launches": int(launches),
         "roofline": {
@@ -611,8 +620,11 @@ def pt_arm(args, env):
             "class_ms_per_pass": dict(zip(names, cms)), "class_launches_per_pass": dict(zip(names, prof["class_launches"][:6])),
             "class_algorithmic_GB": {names[k]: alg_bytes[k] * 1e-9 for k in range(6)},
             "pass_ms_profiled": sum(cms),
-            "note": "algorithmic bytes: traversal = 48 B per ray slot (32 B ray in + 16 B hit out) + 80 B per BVH8 node visited + 48 B per "
-                    "triangle tested; shading = SoA path state read + written per stage (DESIGN.md section 5)",
+            "pass_ms_timed": total_ms / args.steps,
+            "note": "class times come from one profiled pass whose kernels run one by one on one stream; the timed passes overlap "
+                    "wavefronts on two streams, so pass_ms_timed < pass_ms_profiled. Algorithmic bytes: traversal = 48 B per ray "
+                    "(32 B ray in + 16 B hit out, + 4 B queue entry) + 80 B per BVH8 node visited + 48 B per triangle tested; "
+                    "path stages = SoA path state read + written per queue entry (DESIGN.md section 5)",
         },
     }
     if e2e:

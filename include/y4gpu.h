@@ -195,16 +195,18 @@ typedef struct y4gpu_pt_params
 typedef struct y4gpu_pt_stats
 {
 	uint64_t samples;             /* pixel-samples rendered by the last pass */
-	uint64_t rays_closest, rays_shadow;
+	uint64_t rays_closest, rays_shadow;   /* rays actually traced (camera rays + live bounce rays; live shadow rays) */
 	uint64_t kernel_launches;     /* kernels launched by the last pass */
 	double pass_ms;               /* device time of the last pass (CUDA events) */
 	/* filled only when y4gpu_pt_params.profile != 0 */
-	double class_ms[8];           /* 0 fill+camera rays, 1 closest-hit traversal, 2 shadow traversal, 3 hit/bounce shading,
-	                                 4 light sampling + shadow resolve, 5 film splat */
+	double class_ms[8];           /* 0 camera rays, 1 closest-hit traversal, 2 shadow traversal, 3 camera-hit / sub-path start /
+	                                 per-bounce path stages, 4 extra light-sample stages, 5 film splat */
 	uint64_t class_launches[8];
 	uint64_t nodes_closest, tris_closest, nodes_shadow, tris_shadow;   /* BVH8 nodes visited / triangles tested */
 	uint64_t live_closest, live_shadow;                                /* rays with a non-empty interval */
-	uint64_t reserved[4];
+	uint64_t camera_hits;         /* pixel-samples whose camera ray hit a surface and went on (queue of the start stage) */
+	uint64_t path_entries;        /* entries processed by the per-bounce path stages (all bounces, incl. the closing call) */
+	uint64_t reserved[2];
 } y4gpu_pt_stats;
 
 /* Per-triangle material index travels in the flag word of y4gpu_upload_triangles (bits 8..31).

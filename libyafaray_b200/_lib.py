@@ -71,7 +71,8 @@ class PtStats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("pass_ms", C.c_double), ("class_ms", C.c_double * 8), ("class_launches", C.c_uint64 * 8),
                 ("nodes_closest", C.c_uint64), ("tris_closest", C.c_uint64), ("nodes_shadow", C.c_uint64), ("tris_shadow", C.c_uint64),
-                ("live_closest", C.c_uint64), ("live_shadow", C.c_uint64), ("reserved", C.c_uint64 * 4)]  # fmt: skip
+                ("live_closest", C.c_uint64), ("live_shadow", C.c_uint64), ("camera_hits", C.c_uint64), ("path_entries", C.c_uint64),
+                ("reserved", C.c_uint64 * 2)]  # fmt: skip
 
 
 MAT_SHINYDIFFUSE, MAT_LIGHT = 0, 1

@@ -39,7 +39,7 @@ struct Y4Pt
 	cudaEvent_t ev_fork = nullptr;
 	// per-launch counters: 64-bit slots, zeroed once per pass; a queue length is the low word of its slot
 	unsigned long long *d_counters = nullptr, *h_counters = nullptr; size_t counters_cap = 0;
-	std::vector<std::pair<uint32_t, int>> counter_kinds;      // (slot, 0 closest queue / 1 shadow queue) of the last pass
+	std::vector<std::pair<uint32_t, int>> counter_kinds;      // (slot, kind) of the last pass: 0 traced path queue, 1 shadow queue, 2 camera-hit queue, 3 closing path queue
 	uint64_t dense_closest = 0;
 	bool counters_read = true;
 	uint32_t *d_pixel_list = nullptr; uint64_t pixel_list_cap = 0;
@@ -361,9 +361,10 @@ int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out)
 		if(!pt->counters_read)
 		{
 			// queue lengths of the pass (copied to pinned memory before ev1): rays actually traced
-			uint64_t rc = pt->dense_closest, rs = 0;
-			for(const auto &ck : pt->counter_kinds) (ck.second ? rs : rc) += (uint32_t) pt->h_counters[ck.first];
-			pt->stats.rays_closest = rc; pt->stats.rays_shadow = rs;
+			uint64_t sum[4] = {0, 0, 0, 0};
+			for(const auto &ck : pt->counter_kinds) sum[ck.second & 3] += (uint32_t) pt->h_counters[ck.first];
+			pt->stats.rays_closest = pt->dense_closest + sum[0]; pt->stats.rays_shadow = sum[1];
+			pt->stats.camera_hits = sum[2]; pt->stats.path_entries = sum[0] + sum[3];
 			if(pt->params.profile)
 			{
 				pt->stats.nodes_closest = pt->h_counters[0]; pt->stats.tris_closest = pt->h_counters[1]; pt->stats.live_closest = pt->h_counters[2];
@@ -498,7 +499,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		// camera rays -> closest hits -> camera-hit stage with the first light sample
 		Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, ns_local, shard_index, shard_count));
 		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, nullptr, nullptr); pt->dense_closest += W.n;
-		uint32_t *n_hit0 = new_queue_count(-1);
+		uint32_t *n_hit0 = new_queue_count(2);
 		Q.out_q = lane.q_hit0; Q.out_count = n_hit0; Q.sh_q = lane.q_shadow; Q.sh_count = new_queue_count(1);
 		a.l = all_lk.empty() ? -1 : all_lk[0].first;
 		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
@@ -525,7 +526,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 				if(closing && !sc.n_lights) break;                       // nothing waits to be folded in
 				W.ray = ray_buf[depth & 1]; W.ray_next = ray_buf[(depth + 1) & 1];
 				if(!closing) Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, lane.q_path[cur], n_cur);
-				uint32_t *n_next = new_queue_count(depth + 1 < sc.bounces ? 0 : -1);
+				uint32_t *n_next = new_queue_count(depth + 1 < sc.bounces ? 0 : (closing ? -1 : 3));
 				Q.in_q = lane.q_path[cur]; Q.in_count = n_cur; Q.out_q = lane.q_path[cur ^ 1]; Q.out_count = n_next;
 				Q.sh_q = lane.q_shadow; Q.sh_count = new_queue_count(sc.n_lights && !closing ? 1 : -1);
 				a.all_lights = 0; a.depth = depth; a.sub = sub; a.l_prev = -1; a.k_prev = sc.n_lights ? max_ls - 1 : -1;
