@@ -564,14 +564,14 @@ def pt_arm(args, env):
         ye = make()
         ye.upload()
         ye.render_pass(spp * world, 0, 0)
-        ye.read_film()
+        ye.read_film(pinned=True)
         barrier()
         h2d = int(ye._assembled["tris"].nbytes + ye._assembled["flags"].nbytes + 4096)
         t0 = time.perf_counter()
         for k in range(e_steps):
             ye.upload()                                      # host triangles/materials/lights/camera -> device, BVH8 build
             ye.render_pass(spp * world, k * spp * world, 0)
-            fw, frgba = ye.read_film()                       # device -> host film (weights + rgba)
+            fw, frgba = ye.read_film(pinned=True)            # device -> host film (weights + rgba), page-locked staging
         barrier()
         e2e = {"ms": (time.perf_counter() - t0) * 1e3, "steps": e_steps, "h2d": h2d, "d2h": int(fw.nbytes + frgba.nbytes)}
         ye.clearAll()

@@ -57,6 +57,11 @@ class AcceleratorB200:
             msg = self._L.y4gpu_last_error(None)
             self._ctx = C.c_void_p()
             raise Y4Error(f"y4gpu_create failed (rc={rc}): {msg.decode() if msg else ''}")
+        self.rebuild(primitives, flags, leaf_max)
+
+    def rebuild(self, primitives: np.ndarray, flags: Optional[np.ndarray] = None, leaf_max: int = 0) -> None:
+        """Upload a new primitive list into the same context and build its BVH8 (device arrays are reused when the
+        size is unchanged: the per-frame path of an animation or a repeated render)."""
         prims = np.ascontiguousarray(primitives, dtype=np.float32).reshape(-1, 9)
         self.n_primitives = int(prims.shape[0])
         fl = None

@@ -94,14 +94,20 @@ int y4gpu_upload_triangles(y4gpu_ctx *ctx, const float *v_xyz, const uint32_t *f
 	if(n_tri > 0x3fffffffull) { ctx->err = "too many triangles (max 2^30-1)"; return Y4GPU_ERR_ARG; }
 	std::lock_guard<std::mutex> lock(ctx->mtx);
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
-	cudaFree(ctx->d_verts); cudaFree(ctx->d_flags);
-	ctx->d_verts = nullptr; ctx->d_flags = nullptr; ctx->n_tri = 0; ctx->built = false;
+	// a re-upload of the same size (animation frame, repeated render) reuses the device arrays
+	const bool reuse = n_tri && n_tri == ctx->n_tri && ctx->d_verts && (!flags == !ctx->d_flags);
+	ctx->built = false;
+	if(!reuse)
+	{
+		cudaFree(ctx->d_verts); cudaFree(ctx->d_flags);
+		ctx->d_verts = nullptr; ctx->d_flags = nullptr; ctx->n_tri = 0;
+	}
 	if(n_tri == 0) return Y4GPU_OK;
-	Y4_CUDA(ctx, cudaMalloc(&ctx->d_verts, n_tri * 9 * sizeof(float)));
+	if(!reuse) Y4_CUDA(ctx, cudaMalloc(&ctx->d_verts, n_tri * 9 * sizeof(float)));
 	Y4_CUDA(ctx, cudaMemcpyAsync(ctx->d_verts, v_xyz, n_tri * 9 * sizeof(float), cudaMemcpyDefault, ctx->stream));
 	if(flags)
 	{
-		Y4_CUDA(ctx, cudaMalloc(&ctx->d_flags, n_tri * sizeof(uint32_t)));
+		if(!reuse) Y4_CUDA(ctx, cudaMalloc(&ctx->d_flags, n_tri * sizeof(uint32_t)));
 		Y4_CUDA(ctx, cudaMemcpyAsync(ctx->d_flags, flags, n_tri * sizeof(uint32_t), cudaMemcpyDefault, ctx->stream));
 	}
 	Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -15,6 +15,7 @@ struct Y4Pt
 	Y4PtLight *d_lights = nullptr;
 	Y4PtMaterial *d_mats = nullptr;
 	float4 *d_tri_shade = nullptr;
+	uint32_t mats_cap = 0, lights_cap = 0; uint64_t tri_cap = 0, normals_cap = 0; size_t film_cap = 0;
 	float *d_normals = nullptr;
 	uint8_t *d_sigma = nullptr; uint16_t *d_offset = nullptr, *d_prime = nullptr; double *d_inv_prime = nullptr, *d_sigma_d = nullptr; unsigned long long *d_magic = nullptr;
 	bool scene_set = false;
@@ -256,21 +257,21 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		const int ns = y4_light_num_samples(sc, pt->h_lights[i]);
 		if(ns > pt->max_light_samples) pt->max_light_samples = ns;
 	}
-	cudaFree(pt->d_lights); pt->d_lights = nullptr;
+	if(n_light > pt->lights_cap) { cudaFree(pt->d_lights); pt->d_lights = nullptr; pt->lights_cap = 0; }
 	if(n_light)
 	{
-		Y4_CUDA(ctx, cudaMalloc(&pt->d_lights, n_light * sizeof(Y4PtLight)));
+		if(!pt->d_lights) { Y4_CUDA(ctx, cudaMalloc(&pt->d_lights, n_light * sizeof(Y4PtLight))); pt->lights_cap = n_light; }
 		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_lights, pt->h_lights.data(), n_light * sizeof(Y4PtLight), cudaMemcpyHostToDevice, st));
 	}
 	std::vector<Y4PtMaterial> hm(n_mat);
 	for(uint32_t i = 0; i < n_mat; ++i) hm[i] = derive_material(mats[i]);
-	cudaFree(pt->d_mats); pt->d_mats = nullptr;
-	Y4_CUDA(ctx, cudaMalloc(&pt->d_mats, n_mat * sizeof(Y4PtMaterial)));
+	if(n_mat > pt->mats_cap) { cudaFree(pt->d_mats); pt->d_mats = nullptr; pt->mats_cap = 0; }
+	if(!pt->d_mats) { Y4_CUDA(ctx, cudaMalloc(&pt->d_mats, n_mat * sizeof(Y4PtMaterial))); pt->mats_cap = n_mat; }
 	Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_mats, hm.data(), n_mat * sizeof(Y4PtMaterial), cudaMemcpyHostToDevice, st));
-	cudaFree(pt->d_normals); pt->d_normals = nullptr;
+	if(!vertex_normals || ctx->n_tri > pt->normals_cap) { cudaFree(pt->d_normals); pt->d_normals = nullptr; pt->normals_cap = 0; }
 	if(vertex_normals && ctx->n_tri)
 	{
-		Y4_CUDA(ctx, cudaMalloc(&pt->d_normals, ctx->n_tri * 9 * sizeof(float)));
+		if(!pt->d_normals) { Y4_CUDA(ctx, cudaMalloc(&pt->d_normals, ctx->n_tri * 9 * sizeof(float))); pt->normals_cap = ctx->n_tri; }
 		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_normals, vertex_normals, ctx->n_tri * 9 * sizeof(float), cudaMemcpyDefault, st));
 	}
 	if(!pt->d_sigma)
@@ -286,10 +287,10 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		Y4_CUDA(ctx, cudaMemcpy(pt->d_sigma_d, fh.sigma_d.data(), fh.sigma_d.size() * sizeof(double), cudaMemcpyHostToDevice));
 		Y4_CUDA(ctx, cudaMemcpy(pt->d_magic, fh.magic, sizeof(fh.magic), cudaMemcpyHostToDevice));
 	}
-	cudaFree(pt->d_tri_shade); pt->d_tri_shade = nullptr;
+	if(ctx->n_tri > pt->tri_cap) { cudaFree(pt->d_tri_shade); pt->d_tri_shade = nullptr; pt->tri_cap = 0; }
 	if(ctx->n_tri)
 	{
-		Y4_CUDA(ctx, cudaMalloc(&pt->d_tri_shade, ctx->n_tri * sizeof(float4)));
+		if(!pt->d_tri_shade) { Y4_CUDA(ctx, cudaMalloc(&pt->d_tri_shade, ctx->n_tri * sizeof(float4))); pt->tri_cap = ctx->n_tri; }
 		const uint64_t want = (ctx->n_tri + kPtThreads - 1) / kPtThreads, full = (uint64_t) ctx->sm_count * 8u;
 		k_pt_tri_shade<<<(int) (want < full ? want : full), kPtThreads, 0, st>>>(ctx->d_verts, ctx->d_flags, n_mat, ctx->n_tri, pt->d_tri_shade);
 		Y4_CUDA(ctx, cudaGetLastError());
@@ -298,9 +299,13 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	sc.lds.sigma = pt->d_sigma; sc.lds.offset = pt->d_offset; sc.lds.prime = pt->d_prime; sc.lds.inv_prime = pt->d_inv_prime; sc.lds.sigma_d = pt->d_sigma_d; sc.lds.magic = pt->d_magic;
 	// film (internal unless the caller installs buffers)
 	const size_t npx = (size_t) sc.width * sc.height;
-	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); pt->own_film_w = pt->own_film_rgba = nullptr;
-	Y4_CUDA(ctx, cudaMalloc(&pt->own_film_w, npx * sizeof(float)));
-	Y4_CUDA(ctx, cudaMalloc(&pt->own_film_rgba, npx * 4 * sizeof(float)));
+	if(npx != pt->film_cap)
+	{
+		cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); pt->own_film_w = pt->own_film_rgba = nullptr; pt->film_cap = 0;
+		Y4_CUDA(ctx, cudaMalloc(&pt->own_film_w, npx * sizeof(float)));
+		Y4_CUDA(ctx, cudaMalloc(&pt->own_film_rgba, npx * 4 * sizeof(float)));
+		pt->film_cap = npx;
+	}
 	Y4_CUDA(ctx, cudaMemsetAsync(pt->own_film_w, 0, npx * sizeof(float), st));
 	Y4_CUDA(ctx, cudaMemsetAsync(pt->own_film_rgba, 0, npx * 4 * sizeof(float), st));
 	pt->d_film_w = pt->own_film_w; pt->d_film_rgba = pt->own_film_rgba;

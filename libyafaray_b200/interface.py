@@ -58,6 +58,7 @@ class Interface:
         self._next_id = 0
         self.accelerator: Optional[AcceleratorB200] = None
         self.film_buffers = None  # optional (weights, rgba) torch CUDA tensors installed by the caller
+        self._pinned_film = None
         self.last_stats: dict = {}
 
     # ---- the "current ParamMap" (interface.cc:118-181) -------------------------------------------
@@ -343,9 +344,10 @@ class Interface:
     def upload(self):
         """Geometry upload + BVH8 build + scene description (the accelerator/integrator preprocess step)."""
         a = self.assemble()
-        if self.accelerator is not None:
-            self.accelerator.close()
-        self.accelerator = AcceleratorB200(a["tris"], flags=a["flags"], device=self.device)
+        if self.accelerator is not None and self.accelerator.ctx.value:
+            self.accelerator.rebuild(a["tris"], flags=a["flags"])       # same context: device allocations are reused
+        else:
+            self.accelerator = AcceleratorB200(a["tris"], flags=a["flags"], device=self.device)
         L, ctx = self.accelerator._L, self.accelerator.ctx
         nptr = C.c_void_p(a["normals"].ctypes.data) if a["normals"] is not None else None
         _lib.check(ctx, L.y4gpu_pt_set_scene(ctx, C.byref(a["cam"]), a["mats"], a["n_mat"], a["lights"], a["n_light"], C.byref(a["params"]), nptr), "y4gpu_pt_set_scene")
@@ -405,11 +407,18 @@ class Interface:
         for k in acc:
             acc[k] += s[k]
 
-    def read_film(self):
+    def read_film(self, pinned: bool = False):
         """-> (weights [h, w], rgba [h, w, 4]) as accumulated (ImageFilm::weights_ and the Combined layer)."""
         pr = self._assembled["params"]
-        w = np.empty((pr.height, pr.width), np.float32)
-        rgba = np.empty((pr.height, pr.width, 4), np.float32)
+        if pinned:
+            # page-locked staging owned by the interface (reused by the next call): the copy runs at PCIe speed
+            if self._pinned_film is None or self._pinned_film[0].shape != (pr.height, pr.width):
+                self._pinned_film = (_lib.pinned_empty(pr.height * pr.width, np.float32).reshape(pr.height, pr.width),
+                                     _lib.pinned_empty(pr.height * pr.width * 4, np.float32).reshape(pr.height, pr.width, 4))
+            w, rgba = self._pinned_film
+        else:
+            w = np.empty((pr.height, pr.width), np.float32)
+            rgba = np.empty((pr.height, pr.width, 4), np.float32)
         L, ctx = self.accelerator._L, self.accelerator.ctx
         _lib.check(ctx, L.y4gpu_pt_read_film(ctx, C.c_void_p(w.ctypes.data), C.c_void_p(rgba.ctypes.data)), "y4gpu_pt_read_film")
         return w, rgba
