@@ -111,7 +111,9 @@ class AcceleratorB200:
 
     def intersect(self, rays, out=None, counted: bool = False):
         """Closest hit (Accelerator::intersect(ray, t_max) with the wrapper's t_max rule,
-        accelerator.cc:55-67).  rays: [n, 8] (o, tmin, d, tmax); returns HIT_DTYPE records."""
+        accelerator.cc:55-67).  rays: [n, 8] (o, tmin, d, tmax); returns HIT_DTYPE records.
+        Host arrays: synchronous.  Device tensors (rays and `out`): queued on this accelerator's stream and NOT waited
+        for -- call synchronize(), or set_stream() to the stream that produces the rays / consumes the hits."""
         return self._trace(_lib.TRACE_CLOSEST, rays, out, counted)
 
     def isShadowed(self, rays, out=None, counted: bool = False):

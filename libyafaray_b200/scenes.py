@@ -50,9 +50,10 @@ def displaced_sphere(nu: int = 1000, nv: int = 500, seed: int = 0xC3) -> np.ndar
     return np.ascontiguousarray(tris)
 
 
-def triangle_soup(n_tri: int, seed: int = 0xC5) -> np.ndarray:
-    """C5: random triangles, centres uniform in [0,1]^3, edge length log-uniform in [1e-3, 1e-2]."""
-    k = np.arange(n_tri)
+def triangle_soup(n_tri: int, seed: int = 0xC5, first: int = 0) -> np.ndarray:
+    """C5: random triangles, centres uniform in [0,1]^3, edge length log-uniform in [1e-3, 1e-2].
+    `first`: index of the first triangle (elements are hashed from their index, so a large soup can be generated in chunks)."""
+    k = np.arange(first, first + n_tri)
     c = np.stack([hash01(seed, k, np.full_like(k, a)) for a in range(3)], -1)
     size = 1e-3 * np.power(10.0, hash01(seed, k, np.full_like(k, 3)))
     out = np.empty((n_tri, 3, 3))
@@ -149,9 +150,9 @@ def diffuse_rays(p: np.ndarray, n: np.ndarray, ok: np.ndarray, seed: int = 0xD1F
     return rays
 
 
-def incoherent_rays(n: int, seed: int = 0x1C0, lo=0.0, hi=1.0) -> np.ndarray:
+def incoherent_rays(n: int, seed: int = 0x1C0, lo=0.0, hi=1.0, first: int = 0) -> np.ndarray:
     """C5 stress: uniform origins in the cube, uniform directions; tmin=0, unbounded."""
-    k = np.arange(n)
+    k = np.arange(first, first + n)
     o = np.stack([hash01(seed, k, np.full_like(k, a)) for a in range(3)], -1) * (hi - lo) + lo
     z = 2 * hash01(seed, k, np.full_like(k, 3)) - 1
     ph = 2 * np.pi * hash01(seed, k, np.full_like(k, 4))
@@ -164,9 +165,9 @@ def incoherent_rays(n: int, seed: int = 0x1C0, lo=0.0, hi=1.0) -> np.ndarray:
     return rays
 
 
-def segment_rays(n: int, seed: int = 0x5E6, lo=0.0, hi=1.0) -> np.ndarray:
+def segment_rays(n: int, seed: int = 0x5E6, lo=0.0, hi=1.0, first: int = 0) -> np.ndarray:
     """C5 any-hit stress: shadow-style rays between random point pairs (tmin = bias, tmax = dist)."""
-    k = np.arange(n)
+    k = np.arange(first, first + n)
     a = np.stack([hash01(seed, k, np.full_like(k, c)) for c in range(3)], -1) * (hi - lo) + lo
     b = np.stack([hash01(seed, k, np.full_like(k, 3 + c)) for c in range(3)], -1) * (hi - lo) + lo
     d = b - a
