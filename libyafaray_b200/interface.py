@@ -224,30 +224,18 @@ class Interface:
         mat_names = list(self.materials)
         mat_index = {n: i for i, n in enumerate(mat_names)}
         tris, flags, normals, any_normals = [], [], [], False
-        for name in sorted(self.objects):
-            o = self.objects[name]
-            base = self.objects[o.instance_of] if o.instance_of else o
-            vis_o, sh_o = VIS[o.visibility if not o.instance_of else base.visibility]
-            if (not vis_o and not sh_o) or o.is_base:
-                continue
-            if not base.tris:
-                continue
+        base_cache: Dict[str, tuple] = {}      # per mesh: fp32 vertices, index array, flag words, normals (shared by its instances)
+
+        def mesh_arrays(base: _Mesh):
+            if base.name in base_cache:
+                return base_cache[base.name]
+            vis_o, sh_o = VIS[base.visibility]
             v = np.asarray(base.verts, np.float64).astype(np.float32)  # API doubles are narrowed to float (interface.cc:87)
-            if o.instance_of:  # Matrix4 * Point3 in fp32, matrix4.h:85-90
-                m = o.matrix
-                v = np.stack([((m[r, 0] * v[:, 0] + m[r, 1] * v[:, 1]) + m[r, 2] * v[:, 2]) + m[r, 3] for r in range(3)], -1).astype(np.float32)
             idx = np.asarray(base.tris, np.int64)
-            tris.append(v[idx].reshape(-1, 9))
-            if base.normals and len(base.normals) == len(base.verts) and not o.instance_of:
-                nn = np.asarray(base.normals, np.float64).astype(np.float32)
-                normals.append(nn[idx].reshape(-1, 9))
-                any_normals = True
-            else:
-                normals.append(None)
-            f = np.empty(len(idx), np.uint32)
-            for k, mn in enumerate(base.tri_mats):
+            words = {}
+            for mn in set(base.tri_mats):
                 if mn is None:
-                    raise Y4Error(f"object '{name}': triangle without a material")
+                    raise Y4Error(f"object '{base.name}': triangle without a material")
                 vis_m, sh_m = VIS[self.materials[mn].get("visibility", "normal")]
                 w = (mat_index[mn] << _lib.TRI_MAT_SHIFT)
                 if vis_o and vis_m:
@@ -256,7 +244,32 @@ class Interface:
                     w |= _lib.TRI_VIS_SHADOW
                 if sh_m:
                     w |= _lib.TRI_VIS_TSHADOW
-                f[k] = w
+                words[mn] = w
+            f = np.fromiter((words[mn] for mn in base.tri_mats), np.uint32, len(base.tri_mats))
+            nn = None
+            if base.normals and len(base.normals) == len(base.verts):
+                nn = np.asarray(base.normals, np.float64).astype(np.float32)[idx].reshape(-1, 9)
+            base_cache[base.name] = (v, idx, f, nn)
+            return base_cache[base.name]
+
+        for name in sorted(self.objects):
+            o = self.objects[name]
+            base = self.objects[o.instance_of] if o.instance_of else o
+            vis_o, sh_o = VIS[base.visibility]
+            if (not vis_o and not sh_o) or o.is_base:
+                continue
+            if not base.tris:
+                continue
+            v, idx, f, nn = mesh_arrays(base)
+            if o.instance_of:  # Matrix4 * Point3 in fp32, matrix4.h:85-90
+                m = o.matrix
+                v = np.stack([((m[r, 0] * v[:, 0] + m[r, 1] * v[:, 1]) + m[r, 2] * v[:, 2]) + m[r, 3] for r in range(3)], -1).astype(np.float32)
+            tris.append(v[idx].reshape(-1, 9))
+            if nn is not None and not o.instance_of:
+                normals.append(nn)
+                any_normals = True
+            else:
+                normals.append(None)
             flags.append(f)
         if tris:
             T = np.ascontiguousarray(np.concatenate(tris), np.float32)

@@ -162,3 +162,163 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     api.paramsSetString("tiles_order", "linear")
     api.paramsSetInt("tile_size", 32)
     api.setupRender()
+
+
+# ---- C4: instanced city -------------------------------------------------------------------------------
+def _hash01(seed, *idx):
+    from .scenes import hash01
+
+    return hash01(seed, *[np.asarray(i) for i in idx])
+
+
+def _building(seed: int, b: int, n_tri_target: int):
+    """One base "building": unit-footprint box, 4 facades tessellated nx x ny and displaced along their normals, flat roof.
+    -> (verts [n, 3] float64, tris [m, 3] int64); m close to n_tri_target."""
+    height = 1.0 + 5.0 * float(_hash01(seed, b, 0))
+    n_quads = max(4, (n_tri_target - 2) // 8)
+    ny = max(2, int(round(np.sqrt(n_quads * height))))
+    nx = max(2, n_quads // ny)
+    verts, tris = [], []
+    corners = [(-0.5, -0.5), (0.5, -0.5), (0.5, 0.5), (-0.5, 0.5)]
+    for f in range(4):
+        (x0, z0), (x1, z1) = corners[f], corners[(f + 1) % 4]
+        nrm = np.array([z1 - z0, 0.0, -(x1 - x0)])
+        u, v = np.meshgrid(np.arange(nx + 1) / nx, np.arange(ny + 1) / ny, indexing="xy")
+        amp = 0.04 * (u > 0) * (u < 1) * (v > 0) * (v < 1)      # facade edges stay put so the faces close up
+        d = (_hash01(seed, np.full(u.shape, b * 8 + f), (v * ny).astype(np.int64) * 4099 + (u * nx).astype(np.int64)) - 0.5) * amp
+        p = np.stack([x0 + (x1 - x0) * u, height * v, z0 + (z1 - z0) * u], -1) + d[..., None] * nrm
+        base = len(verts)
+        verts.extend(p.reshape(-1, 3).tolist())
+        ii, jj = np.meshgrid(np.arange(nx), np.arange(ny), indexing="xy")
+        a = base + jj * (nx + 1) + ii
+        q = np.stack([a, a + 1, a + nx + 2, a, a + nx + 2, a + nx + 1], -1).reshape(-1, 3)
+        tris.extend(q.tolist())
+    base = len(verts)
+    verts.extend([(-0.5, height, -0.5), (0.5, height, -0.5), (0.5, height, 0.5), (-0.5, height, 0.5)])
+    tris.extend([(base, base + 2, base + 1), (base, base + 3, base + 2)])
+    return np.asarray(verts, np.float64), np.asarray(tris, np.int64)
+
+
+def _bulk_mesh(api, name, material, verts, tris, base_object=False):
+    api.paramsClearAll()
+    api.paramsSetString("type", "mesh")
+    api.paramsSetInt("num_vertices", len(verts))
+    api.paramsSetInt("num_faces", len(tris))
+    if base_object:
+        api.paramsSetBool("is_base_object", True)
+    api.createObject(name)
+    api.setCurrentMaterial(material)
+    if "add_mesh_arrays" in dir(api):
+        api.add_mesh_arrays(verts, tris)
+    else:
+        for v in verts:
+            api.addVertex(float(v[0]), float(v[1]), float(v[2]))
+        for t in tris:
+            api.addTriangle(int(t[0]), int(t[1]), int(t[2]))
+    api.endObject()
+
+
+def city(api, n_tri_target=10_000_000, width=3840, height=2160, spp=16, bounces=8, seed=0xC4, n_base=64, grid=128,
+         tri_range=(2000, 40000), threads=1, accelerator="yafaray-kdtree-original", filter_type="box", light_samples=1):
+    """C4: `n_base` base building meshes instanced (yafaray_addInstance, flattened by the scene like the reference does)
+    on a jittered `grid` x `grid` lattice with random yaw / scale until `n_tri_target` instanced triangles, a ground quad,
+    one large sun-like area light, constant sky.  -> number of instanced triangles."""
+    cols = [(0.70, 0.68, 0.64), (0.55, 0.36, 0.30), (0.45, 0.50, 0.58), (0.80, 0.76, 0.60)]
+    for i, c in enumerate(cols):
+        _material(api, "wall%d" % i, c)
+    _material(api, "ground", (0.35, 0.36, 0.34))
+    api.startGeometry()
+    counts = []
+    for b in range(n_base):
+        lo, hi = tri_range
+        target = int(lo * (hi / lo) ** float(_hash01(seed, b, 1)))
+        v, t = _building(seed, b, target)
+        counts.append(len(t))
+        _bulk_mesh(api, "base%02d" % b, "wall%d" % (b % len(cols)), v, t, base_object=True)
+    ext = float(grid)
+    v, t = _quad((-2.0, 0.0, -2.0), (-2.0, 0.0, ext + 2.0), (ext + 2.0, 0.0, ext + 2.0), (ext + 2.0, 0.0, -2.0))
+    _mesh(api, "a_ground", "ground", v, t)
+    total, k = 2, 0
+    while total < n_tri_target and k < grid * grid:
+        # visit lattice cells in a fixed pseudo-random order so a small target still spreads over the whole city
+        cell = (k * 7919) % (grid * grid)
+        gx, gz = cell % grid, cell // grid
+        b = int(_hash01(seed, k, 2) * n_base) % n_base
+        yaw = 2.0 * np.pi * float(_hash01(seed, k, 3))
+        sc = 0.55 + 0.35 * float(_hash01(seed, k, 4))
+        cx = gx + 0.5 + 0.2 * (float(_hash01(seed, k, 5)) - 0.5)
+        cz = gz + 0.5 + 0.2 * (float(_hash01(seed, k, 6)) - 0.5)
+        c, s = np.cos(yaw) * sc, np.sin(yaw) * sc
+        m = [c, 0.0, s, cx, 0.0, sc, 0.0, 0.0, -s, 0.0, c, cz, 0.0, 0.0, 0.0, 1.0]
+        api.addInstance("base%02d" % b, *[float(x) for x in m])
+        total += counts[b]
+        k += 1
+    api.endGeometry()
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "arealight")            # sun-like: a big quad high above, tilted, emitting downwards
+    h = 0.9 * ext
+    api.paramsSetVector("corner", 0.15 * ext, h, 0.15 * ext)
+    api.paramsSetVector("point1", 0.45 * ext, h, 0.15 * ext)
+    api.paramsSetVector("point2", 0.15 * ext, h + 0.1 * ext, 0.45 * ext)
+    api.paramsSetColor("color", 1.0, 0.96, 0.9, 1.0)
+    api.paramsSetFloat("power", 60.0)
+    api.paramsSetInt("samples", light_samples)
+    api.createLight("sun")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "perspective")
+    api.paramsSetVector("from", -0.12 * ext, 0.22 * ext, -0.12 * ext)
+    api.paramsSetVector("to", 0.45 * ext, 0.0, 0.45 * ext)
+    api.paramsSetVector("up", -0.12 * ext, 0.22 * ext + 1.0, -0.12 * ext)
+    api.paramsSetInt("resx", width)
+    api.paramsSetInt("resy", height)
+    api.paramsSetFloat("focal", 1.2)
+    api.createCamera("cam")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "constant")
+    api.paramsSetColor("color", 0.45, 0.6, 0.85, 1.0)
+    api.createBackground("bg")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "pathtracing")
+    api.paramsSetInt("bounces", bounces)
+    api.paramsSetInt("path_samples", 1)
+    api.paramsSetInt("russian_roulette_min_bounces", bounces)
+    api.paramsSetString("caustic_type", "none")
+    api.paramsSetInt("raydepth", 2)
+    api.createIntegrator("pt")
+
+    api.paramsClearAll()
+    api.paramsSetString("camera_name", "cam")
+    api.createRenderView("view")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "combined")
+    api.paramsSetString("image_type", "ColorAlpha")
+    api.paramsSetString("exported_image_type", "ColorAlpha")
+    api.paramsSetString("exported_image_name", "Combined")
+    api.defineLayer()
+
+    api.paramsClearAll()
+    api.paramsSetString("integrator_name", "pt")
+    api.paramsSetString("background_name", "bg")
+    api.paramsSetString("scene_accelerator", accelerator)
+    api.paramsSetInt("width", width)
+    api.paramsSetInt("height", height)
+    api.paramsSetInt("threads", threads)
+    api.paramsSetInt("AA_passes", 1)
+    api.paramsSetInt("AA_minsamples", spp)
+    api.paramsSetInt("AA_inc_samples", 1)
+    api.paramsSetFloat("AA_pixelwidth", 1.5)
+    api.paramsSetString("filter_type", filter_type)
+    api.paramsSetString("tiles_order", "linear")
+    api.paramsSetInt("tile_size", 32)
+    api.setupRender()
+    return total
+
+
+def build(api, scene="cornell", **kw):
+    """Dispatch by scene name (the committed golden configurations carry a `scene` key)."""
+    return {"cornell": cornell_box, "city": city}[scene](api, **kw)

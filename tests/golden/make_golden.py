@@ -7,6 +7,7 @@ from /root/reference by `make -C oracle ref`).  Run in the build container only:
   rays_sphere.npz    <- oracle/_ref/ref_raybatch on scenes.displaced_sphere(40, 20): primary,
                         shadow and diffuse batches with the reference kd-tree's hit records
   rays_soup.npz      <- same on scenes.triangle_soup(3000) with incoherent + segment rays
+  pt_city.npz        <- the same harness on scenes_pt.city (instanced buildings) for PT_GOLDEN_CITY
   pt_cornell.npz     <- oracle/_ref/ref_render (reference PathIntegrator + kd-tree through the C API,
                         threads=1, tiles linear) on scenes_pt.cornell_box for the PT_GOLDEN configurations
 """
@@ -30,6 +31,21 @@ PT_GOLDEN = {
     "point_gauss": dict(width=96, height=54, spp=4, bounces=4, point_light=True, filter_type="gauss"),
     "area3_oren_paths2": dict(width=64, height=36, spp=3, bounces=3, light_samples=3, oren_nayar=True, path_samples=2),
 }
+# C4 in miniature (instanced buildings through yafaray_addInstance, sky background, gauss filter) -> pt_city.npz
+PT_GOLDEN_CITY = {
+    "city_small": dict(scene="city", n_tri_target=6000, n_base=4, grid=6, tri_range=(300, 900), width=80, height=45, spp=3, bounces=4, filter_type="gauss"),
+}
+
+
+def make_city():
+    from libyafaray_b200 import scenes_pt
+
+    out = {}
+    for key, kw in PT_GOLDEN_CITY.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.build(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+    np.savez_compressed(os.path.join(HERE, "pt_city.npz"), **out)
 
 
 def main():
@@ -66,6 +82,7 @@ def main():
         scenes_pt.cornell_box(rec, **kw)
         out[key] = helpers.ref_render(rec)[0]
     np.savez_compressed(os.path.join(HERE, "pt_cornell.npz"), **out)
+    make_city()
     print("golden fixtures written")
 
 

@@ -13,24 +13,26 @@ from libyafaray_b200 import interface, scenes_pt
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 sys.path.insert(0, GOLD)
-from make_golden import PT_GOLDEN  # noqa: E402
+from make_golden import PT_GOLDEN, PT_GOLDEN_CITY  # noqa: E402
+
+ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: ("pt_city.npz", v) for k, v in PT_GOLDEN_CITY.items()}}
 
 PSNR_MIN = 50.0  # BASELINE.json north_star: PSNR >= 50 dB at equal spp with identical sample sequences
 
 
 def _gpu(shard_index=0, shard_count=1, **kw):
     yi = interface.Interface(shard_index=shard_index, shard_count=shard_count)
-    scenes_pt.cornell_box(yi, accelerator="yafaray-b200-bvh8", **kw)
+    scenes_pt.build(yi, accelerator="yafaray-b200-bvh8", **kw)
     return yi
 
 
-@pytest.mark.parametrize("key", sorted(PT_GOLDEN))
+@pytest.mark.parametrize("key", sorted(ALL_GOLDEN))
 def test_gpu_vs_golden_reference_render(key):
-    ref = np.load(os.path.join(GOLD, "pt_cornell.npz"))[key]
-    yi = _gpu(**PT_GOLDEN[key])
+    ref = np.load(os.path.join(GOLD, ALL_GOLDEN[key][0]))[key]
+    yi = _gpu(**ALL_GOLDEN[key][1])
     img = yi.render()
     assert helpers.psnr(img, ref) >= PSNR_MIN
-    assert np.abs(img - ref).max() <= 1e-5 * max(1.0, float(ref.max()))
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max()))
     assert yi.last_stats["kernel_launches"] > 0 and yi.last_stats["rays_closest"] > 0
 
 
