@@ -209,6 +209,19 @@ typedef struct y4gpu_pt_stats
 	uint64_t reserved[2];
 } y4gpu_pt_stats;
 
+/* Noise-detection parameters of adaptive anti-aliasing (AaNoiseParams, include/common/aa_noise_params.h:27-46;
+ * render parameters AA_threshold, AA_detect_color_noise, AA_dark_detection_type, AA_dark_threshold_factor,
+ * AA_variance_edge_size, AA_variance_pixels; scene.cc:586-595). */
+typedef struct y4gpu_pt_aa_noise
+{
+	float threshold;              /* current AA threshold (the host adapts it between passes like TiledIntegrator::render) */
+	int32_t detect_color_noise;
+	int32_t dark_detection_type;  /* 0 none, 1 linear (the "curve" type is not supported) */
+	float dark_threshold_factor;
+	int32_t variance_edge_size, variance_pixels;
+	int32_t reserved[6];
+} y4gpu_pt_aa_noise;
+
 /* Per-triangle material index travels in the flag word of y4gpu_upload_triangles (bits 8..31).
  * vertex_normals: n_tri*9 floats (exported normals: shading normal interpolated like
  * primitive_triangle.cc:104-114) or NULL for flat shading. */
@@ -225,6 +238,13 @@ int y4gpu_pt_clear_film(y4gpu_ctx *ctx);
 int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, int aa_pass_number,
                          const uint32_t *pixel_list, uint64_t n_pixels, int shard_index, int shard_count);
 /* Film as accumulated (NOT normalised): weights h*w, rgba h*w*4; host or device destinations. */
+/* ImageFilm::nextPass(adaptive_aa = true) on the device (imagefilm.cc:259-445): flags the pixels whose normalised colour
+ * differs from a neighbour's by at least the threshold (plus never-sampled pixels and the variance window rule) and
+ * compacts them, in raster order, into a device-resident pixel list for y4gpu_pt_render_pass.
+ * d_weights / d_rgba: the ACCUMULATED film to analyse (NULL = the context's film; multi-GPU callers pass the all-reduced
+ * total).  *d_pixel_list stays valid until the next call; *n_resample is ImageFilm::nextPass's return value. */
+int y4gpu_pt_next_pass(y4gpu_ctx *ctx, const y4gpu_pt_aa_noise *aa, const float *d_weights, const float *d_rgba,
+                       const uint32_t **d_pixel_list, uint64_t *n_resample);
 int y4gpu_pt_read_film(y4gpu_ctx *ctx, float *weights, float *rgba);
 int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out);
 

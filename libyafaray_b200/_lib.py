@@ -75,6 +75,11 @@ class PtStats(C.Structure):
                 ("reserved", C.c_uint64 * 2)]  # fmt: skip
 
 
+class PtAaNoise(C.Structure):
+    _fields_ = [("threshold", C.c_float), ("detect_color_noise", C.c_int32), ("dark_detection_type", C.c_int32), ("dark_threshold_factor", C.c_float),
+                ("variance_edge_size", C.c_int32), ("variance_pixels", C.c_int32), ("reserved", C.c_int32 * 6)]  # fmt: skip
+
+
 MAT_SHINYDIFFUSE, MAT_LIGHT = 0, 1
 LIGHT_POINT, LIGHT_AREA = 0, 1
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
@@ -94,7 +99,7 @@ EXPORTED = [
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow",
     "y4gpu_get_stats", "y4gpu_synchronize",
     "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
-    "y4gpu_pt_read_film", "y4gpu_pt_get_stats",
+    "y4gpu_pt_read_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass",
 ]  # fmt: skip
 
 
@@ -145,6 +150,8 @@ def lib() -> C.CDLL:
     L.y4gpu_pt_clear_film.restype = i32
     L.y4gpu_pt_render_pass.argtypes = [vp, i32, i32, i32, vp, u64, i32, i32]
     L.y4gpu_pt_render_pass.restype = i32
+    L.y4gpu_pt_next_pass.argtypes = [vp, vp, vp, vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
+    L.y4gpu_pt_next_pass.restype = i32
     L.y4gpu_pt_read_film.argtypes = [vp, vp, vp]
     L.y4gpu_pt_read_film.restype = i32
     L.y4gpu_pt_get_stats.argtypes = [vp, C.POINTER(PtStats)]

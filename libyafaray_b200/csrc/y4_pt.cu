@@ -3,6 +3,8 @@
 #include "y4_ctx.h"
 #include "y4_pt_stages.cuh"
 #include "y4_faure.h"
+#include "y4_film.cuh"
+#include <cub/cub.cuh>
 #include <cstring>
 #include <vector>
 
@@ -44,6 +46,9 @@ struct Y4Pt
 	uint64_t dense_closest = 0;
 	bool counters_read = true;
 	uint32_t *d_pixel_list = nullptr; uint64_t pixel_list_cap = 0;
+	// adaptive AA: per-pixel resample flags, their compacted raster-order list, CUB scratch
+	uint8_t *d_aa_flags = nullptr; uint32_t *d_aa_list = nullptr; uint64_t *d_aa_count = nullptr; void *d_aa_tmp = nullptr;
+	size_t aa_cap = 0, aa_tmp_bytes = 0;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	std::vector<cudaEvent_t> prof_events;     // profile mode: one event after every launch
 	y4gpu_pt_stats stats = {};
@@ -130,6 +135,17 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_tri_shade(const float *__rest
 	for(uint64_t t = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x; t < n_tri; t += (uint64_t) gridDim.x * blockDim.x) out[t] = y4_tri_shade(verts, tri_flags, n_mats, t);
 }
 
+__global__ void __launch_bounds__(kPtThreads) k_film_flag_init(const float *__restrict__ weights, uint8_t *flags, size_t n)
+{
+	for(size_t p = blockIdx.x * (size_t) blockDim.x + threadIdx.x; p < n; p += (size_t) gridDim.x * blockDim.x) y4_film_flag_init(weights, flags, p);
+}
+__global__ void __launch_bounds__(kPtThreads) k_film_flag_detect(const float *__restrict__ weights, const float *__restrict__ rgba, int width, int height, y4gpu_pt_aa_noise aa, uint8_t *flags)
+{
+	const size_t n = (size_t) (width - 1) * (size_t) (height - 1);
+	for(size_t q = blockIdx.x * (size_t) blockDim.x + threadIdx.x; q < n; q += (size_t) gridDim.x * blockDim.x)
+		y4_film_flag_detect(weights, rgba, width, height, aa, flags, (int) (q % (size_t) (width - 1)), (int) (q / (size_t) (width - 1)));
+}
+
 __global__ void __launch_bounds__(kPtThreads) k_pt_splat(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, float *film_w, float *film_rgba)
 {
 	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x) y4_pt_finish_splat(sc, W, ps, i, film_w, film_rgba);
@@ -203,6 +219,7 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime); cudaFree(pt->d_sigma_d); cudaFree(pt->d_magic);
 	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); cudaFree(pt->d_pixel_list);
 	cudaFree(pt->d_counters); cudaFreeHost(pt->h_counters);
+	cudaFree(pt->d_aa_flags); cudaFree(pt->d_aa_list); cudaFree(pt->d_aa_count); cudaFree(pt->d_aa_tmp);
 	if(pt->ev0) cudaEventDestroy(pt->ev0);
 	if(pt->ev1) cudaEventDestroy(pt->ev1);
 	for(cudaEvent_t e : pt->prof_events) cudaEventDestroy(e);
@@ -352,6 +369,53 @@ int y4gpu_pt_read_film(y4gpu_ctx *ctx, float *weights, float *rgba)
 	Y4_CUDA(ctx, cudaMemcpyAsync(weights, pt->d_film_w, npx * sizeof(float), cudaMemcpyDefault, ctx->stream));
 	Y4_CUDA(ctx, cudaMemcpyAsync(rgba, pt->d_film_rgba, npx * 4 * sizeof(float), cudaMemcpyDefault, ctx->stream));
 	Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return Y4GPU_OK;
+}
+
+int y4gpu_pt_next_pass(y4gpu_ctx *ctx, const y4gpu_pt_aa_noise *aa, const float *d_weights, const float *d_rgba,
+                       const uint32_t **d_pixel_list, uint64_t *n_resample)
+{
+	if(!ctx || !aa || !d_pixel_list || !n_resample || (!d_weights != !d_rgba)) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4Pt *pt = ctx->pt;
+	if(!pt || !pt->scene_set) { ctx->err = "y4gpu_pt_next_pass before y4gpu_pt_set_scene"; return Y4GPU_ERR_ARG; }
+	if(aa->dark_detection_type != 0 && aa->dark_detection_type != 1) { ctx->err = "AA_dark_detection_type 'curve' is not supported by the GPU back end"; return Y4GPU_ERR_UNSUPPORTED; }
+	if(d_weights && (!pt_is_device_ptr(d_weights) || !pt_is_device_ptr(d_rgba))) { ctx->err = "film buffers must be device memory"; return Y4GPU_ERR_ARG; }
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	cudaStream_t st = ctx->stream;
+	const int width = pt->h_scene.width, height = pt->h_scene.height;
+	const size_t npx = (size_t) width * height;
+	const float *w = d_weights ? d_weights : pt->d_film_w, *rgba = d_rgba ? d_rgba : pt->d_film_rgba;
+	if(npx > pt->aa_cap)
+	{
+		cudaFree(pt->d_aa_flags); cudaFree(pt->d_aa_list); pt->d_aa_flags = nullptr; pt->d_aa_list = nullptr; pt->aa_cap = 0;
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_aa_flags, npx));
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_aa_list, npx * sizeof(uint32_t)));
+		pt->aa_cap = npx;
+	}
+	if(!pt->d_aa_count) Y4_CUDA(ctx, cudaMalloc(&pt->d_aa_count, sizeof(uint64_t)));
+	const int grid = pt_grid(ctx, (uint32_t) (npx < 0xffffffffull ? npx : 0xffffffffull));
+	k_film_flag_init<<<grid, kPtThreads, 0, st>>>(w, pt->d_aa_flags, npx);
+	if(width > 1 && height > 1) k_film_flag_detect<<<grid, kPtThreads, 0, st>>>(w, rgba, width, height, *aa, pt->d_aa_flags);
+	Y4_CUDA(ctx, cudaGetLastError());
+	// raster-order compaction of the flagged pixel indices
+	cub::CountingInputIterator<uint32_t> idx(0u);
+	size_t need = 0;
+	Y4_CUDA(ctx, cub::DeviceSelect::Flagged(nullptr, need, idx, pt->d_aa_flags, pt->d_aa_list, pt->d_aa_count, (int) npx, st));
+	if(need > pt->aa_tmp_bytes)
+	{
+		cudaFree(pt->d_aa_tmp); pt->d_aa_tmp = nullptr; pt->aa_tmp_bytes = 0;
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_aa_tmp, need));
+		pt->aa_tmp_bytes = need;
+	}
+	need = pt->aa_tmp_bytes;
+	Y4_CUDA(ctx, cub::DeviceSelect::Flagged(pt->d_aa_tmp, need, idx, pt->d_aa_flags, pt->d_aa_list, pt->d_aa_count, (int) npx, st));
+	uint64_t count = 0;
+	Y4_CUDA(ctx, cudaMemcpyAsync(&count, pt->d_aa_count, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	ctx->stats.kernel_launches += 3;
+	*d_pixel_list = pt->d_aa_list;
+	*n_resample = count;
 	return Y4GPU_OK;
 }
 

@@ -375,6 +375,8 @@ class Interface:
         L, ctx = self.accelerator._L, self.accelerator.ctx
         if pixel_list is None:
             ptr, n = None, 0
+        elif isinstance(pixel_list, tuple):          # (device pointer, count) from next_pass()
+            ptr, n = pixel_list
         elif hasattr(pixel_list, "data_ptr"):
             ptr, n = C.c_void_p(pixel_list.data_ptr()), int(pixel_list.numel())
         else:
@@ -382,26 +384,71 @@ class Interface:
             ptr, n = C.c_void_p(pixel_list.ctypes.data), int(pixel_list.size)
         _lib.check(ctx, L.y4gpu_pt_render_pass(ctx, int(n_samples), int(offset), int(aa_pass), ptr, n, self.shard_index, self.shard_count), "y4gpu_pt_render_pass")
 
+    def aa_noise_params(self, threshold=None) -> "_lib.PtAaNoise":
+        """AaNoiseParams of the render parameters (scene.cc:586-595), optionally with the adapted threshold."""
+        rp = self.render_params
+        aa = _lib.PtAaNoise()
+        aa.threshold = float(rp.get("AA_threshold", 0.05)) if threshold is None else float(threshold)
+        aa.detect_color_noise = int(bool(rp.get("AA_detect_color_noise", False)))
+        ddt = str(rp.get("AA_dark_detection_type", "none"))
+        if ddt == "curve":
+            raise Y4Error("AA_dark_detection_type 'curve' is not supported by the GPU back end")
+        aa.dark_detection_type = 1 if ddt == "linear" else 0
+        aa.dark_threshold_factor = float(rp.get("AA_dark_threshold_factor", 0.0))
+        aa.variance_edge_size, aa.variance_pixels = int(rp.get("AA_variance_edge_size", 10)), int(rp.get("AA_variance_pixels", 0))
+        return aa
+
+    def next_pass(self, aa, film=None):
+        """ImageFilm::nextPass(adaptive) on the device -> (device pixel-list pointer, n_resample).
+        film: optional (weights, rgba) torch CUDA tensors holding the accumulated film (multi-GPU: the all-reduced total)."""
+        L, ctx = self.accelerator._L, self.accelerator.ctx
+        ptr, n = C.c_void_p(), C.c_uint64()
+        fw = C.c_void_p(film[0].data_ptr()) if film is not None else None
+        fr = C.c_void_p(film[1].data_ptr()) if film is not None else None
+        _lib.check(ctx, L.y4gpu_pt_next_pass(ctx, C.byref(aa), fw, fr, C.byref(ptr), C.byref(n)), "y4gpu_pt_next_pass")
+        return ptr, int(n.value)
+
     def render(self, monitor_callback=None):
-        """yafaray_render: pass 0 with AA_minsamples, then AA_passes-1 passes of ceil(AA_inc_samples * mult)
-        samples over all pixels (adaptive resampling by ImageFilm::nextPass is a host-side 'next' row: with
-        AA_threshold > 0 and AA_passes > 1 the render is refused).  Returns the normalised Combined layer."""
+        """yafaray_render = TiledIntegrator::render (integrator_tiled.cc:97-234): pass 0 with AA_minsamples over every
+        pixel, then AA_passes-1 passes of ceil(AA_inc_samples * mult) samples.  With AA_threshold > 0 the later passes
+        are adaptive: ImageFilm::nextPass flags the noisy pixels (on the device), only those are resampled, and the
+        threshold is lowered when fewer than AA_resampled_floor % of the pixels were flagged -- the reference's loop,
+        including its fp32 arithmetic.  Returns the normalised Combined layer."""
         a = self.upload()
         pr, rp = a["params"], self.render_params
-        if pr.aa_passes > 1 and float(rp.get("AA_threshold", 0.05)) > 0.0:
-            raise Y4Error("adaptive multi-pass AA (AA_threshold > 0) is not supported by the GPU back end yet; set AA_threshold = 0")
+        f32 = np.float32
         L, ctx = self.accelerator._L, self.accelerator.ctx
         _lib.check(ctx, L.y4gpu_pt_clear_film(ctx), "y4gpu_pt_clear_film")
         stats = {"samples": 0, "rays_closest": 0, "rays_shadow": 0, "kernel_launches": 0, "pass_ms": 0.0}
         self.render_pass(pr.aa_samples, 0, 0)
         self._add_stats(stats)
-        acum, mult = pr.aa_samples, np.float32(1.0)
+        threshold = f32(rp.get("AA_threshold", 0.05))
+        floor_pixels = int(np.floor(f32(f32(rp.get("AA_resampled_floor", 0.0)) * f32(pr.width * pr.height)) / f32(100.0)))
+        acum, mult = pr.aa_samples, f32(1.0)
+        resampled, threshold_changed = 0, True
+        self.resampled_per_pass = []
         for i in range(1, pr.aa_passes):
-            mult = np.float32(mult * np.float32(pr.aa_sample_multiplier_factor))
-            n = int(np.ceil(np.float32(pr.aa_inc_samples) * mult))
-            self.render_pass(n, acum, i)
-            self._add_stats(stats)
+            mult = f32(mult * f32(pr.aa_sample_multiplier_factor))
+            plist, skip = None, False
+            if resampled <= 0 and not threshold_changed:
+                skip = True                                     # nothing was resampled and the threshold did not move
+            elif threshold > 0:
+                ptr, resampled = self.next_pass(self.aa_noise_params(threshold))
+                plist = (ptr, resampled)
+                threshold_changed = False
+            else:
+                resampled, threshold_changed = pr.width * pr.height, False     # non-adaptive: every pixel
+            self.resampled_per_pass.append(0 if skip else resampled)
+            n = int(np.ceil(f32(pr.aa_inc_samples) * mult))
+            if not skip and resampled > 0:
+                self.render_pass(n, acum, i, pixel_list=plist)
+                self._add_stats(stats)
             acum += n
+            if resampled < floor_pixels:
+                ratio = min(f32(8.0), f32(floor_pixels) / f32(resampled)) if resampled > 0 else f32(8.0)
+                threshold = f32(threshold * f32(f32(1.0) - f32(0.1) * ratio))
+                if threshold > 0:
+                    threshold_changed = True
         self.last_stats = stats
         return self.read_image()
 

@@ -5,6 +5,7 @@
 #include "../../libyafaray_b200/csrc/y4_trace.cuh"
 #include "../../libyafaray_b200/csrc/y4_pt_host.h"
 #include "../../libyafaray_b200/csrc/y4_faure.h"
+#include "../../libyafaray_b200/csrc/y4_film.cuh"
 #include <vector>
 
 struct EmuBvh
@@ -41,7 +42,8 @@ static void push(uint32_t mask, uint32_t i, uint32_t n, std::vector<uint32_t> *p
 
 extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material *mats, uint32_t n_mat, const y4gpu_pt_light *lights, uint32_t n_light,
                              const y4gpu_pt_params *params, const float *verts, const uint32_t *flags, int n_tri, const float *normals,
-                             int n_samples, int offset, int aa_pass, int shard_index, int shard_count, float *film_w, float *film_rgba)
+                             int n_samples, int offset, int aa_pass, int shard_index, int shard_count, float *film_w, float *film_rgba,
+                             const uint32_t *pixel_list, uint64_t n_pixels)
 {
 	EmuBvh b;
 	emu_build(verts, flags, n_tri, 1, b);
@@ -73,7 +75,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 
 	// same pixel-sample enumeration as k_pt_fill (y4_pt.cu)
 	const uint32_t ns_local = shard_index < n_samples ? (uint32_t) ((n_samples - shard_index + shard_count - 1) / shard_count) : 0u;
-	const uint32_t n = (uint32_t) sc.width * sc.height * ns_local;
+	const uint32_t n = (uint32_t) (pixel_list ? n_pixels : (uint64_t) sc.width * sc.height) * ns_local;
 	if(n == 0) return 0;
 	std::vector<uint32_t> pix(n), samp(n), fl(n), lnum(n);
 	std::vector<float4> col(n), pcol(n), thr(n), pthr(n), lcol(n), acc_a(n), acc_b(n), lsamp(n), scontrib(2ull * n);
@@ -84,7 +86,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	W.col = &col[0].x; W.pcol = &pcol[0].x; W.thr = &thr[0].x; W.lcol = &lcol[0].x; W.acc_a = &acc_a[0].x; W.acc_b = &acc_b[0].x; W.lsamp = &lsamp[0].x; W.pthr = &pthr[0].x;
 	W.ray = ray.data(); W.ray_next = ray2.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = &scontrib[0].x;
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
-	for(uint32_t i = 0; i < n; ++i) { pix[i] = i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
+	for(uint32_t i = 0; i < n; ++i) { pix[i] = pixel_list ? pixel_list[i / ns_local] : i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
 	// same stage sequence as y4gpu_pt_render_pass (y4_pt.cu), queues as vectors
 	for(uint32_t i = 0; i < n; ++i) y4_pt_gen(sc, W, ps, i);
 	trace(bvh, Y4_TRACE_CLOSEST, W.ray, nullptr, n, W.hit);
@@ -132,4 +134,16 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	W.ray = ray_buf[0];
 	for(uint32_t i = 0; i < n; ++i) y4_pt_finish_splat(sc, W, ps, i, film_w, film_rgba);
 	return 0;
+}
+
+// ImageFilm::nextPass(adaptive) flags, the two phases of y4gpu_pt_next_pass as serial loops
+extern "C" uint64_t emu_film_flags(const float *weights, const float *rgba, int width, int height, const y4gpu_pt_aa_noise *aa, uint8_t *flags)
+{
+	const size_t npx = (size_t) width * height;
+	for(size_t p = 0; p < npx; ++p) y4_film_flag_init(weights, flags, p);
+	for(int y = 0; y < height - 1; ++y)
+		for(int x = 0; x < width - 1; ++x) y4_film_flag_detect(weights, rgba, width, height, *aa, flags, x, y);
+	uint64_t n = 0;
+	for(size_t p = 0; p < npx; ++p) n += flags[p];
+	return n;
 }

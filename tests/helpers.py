@@ -90,19 +90,36 @@ from refserver import RefServer  # noqa: E402,F401
 from refserver import ScriptRecorder, ref_render  # noqa: E402,F401
 
 
-def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0, shard_index=0, shard_count=1):
-    """CPU emulation of the wavefront path tracer stages on an Interface.assemble() result -> (weights, rgba)."""
+def emu_film_flags(a, w, rgba, aa):
+    """CPU emulation of y4gpu_pt_next_pass: -> flagged pixel indices (raster order)."""
+    import ctypes as C
+
+    pr = a["params"]
+    flags = np.zeros(pr.height * pr.width, np.uint8)
+    f = emu().emu_film_flags
+    f.restype = C.c_uint64
+    n = f(_p(np.ascontiguousarray(w, np.float32)), _p(np.ascontiguousarray(rgba, np.float32)), C.c_int(pr.width), C.c_int(pr.height), C.byref(aa), _p(flags))
+    idx = np.nonzero(flags)[0].astype(np.uint32)
+    assert len(idx) == n
+    return idx
+
+
+def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0, shard_index=0, shard_count=1, pixel_list=None, film=None):
+    """CPU emulation of the wavefront path tracer stages on an Interface.assemble() result -> (weights, rgba).
+    pixel_list: adaptive pass over these pixels only; film: (weights, rgba) to accumulate into."""
     import ctypes as C
 
     pr = a["params"]
     n_samples = pr.aa_samples if n_samples is None else n_samples
-    w = np.zeros((pr.height, pr.width), np.float32)
-    rgba = np.zeros((pr.height, pr.width, 4), np.float32)
+    w = np.zeros((pr.height, pr.width), np.float32) if film is None else film[0]
+    rgba = np.zeros((pr.height, pr.width, 4), np.float32) if film is None else film[1]
+    pl = None if pixel_list is None else np.ascontiguousarray(pixel_list, np.uint32)
     f = emu().emu_pt_render
     f.restype = C.c_int
     nptr = a["normals"].ctypes.data_as(C.c_void_p) if a["normals"] is not None else None
     rc = f(C.byref(a["cam"]), a["mats"], C.c_uint32(a["n_mat"]), a["lights"], C.c_uint32(a["n_light"]), C.byref(pr), _p(a["tris"]), _p(a["flags"]),
-           C.c_int(len(a["tris"])), nptr, C.c_int(n_samples), C.c_int(offset), C.c_int(aa_pass), C.c_int(shard_index), C.c_int(shard_count), _p(w), _p(rgba))
+           C.c_int(len(a["tris"])), nptr, C.c_int(n_samples), C.c_int(offset), C.c_int(aa_pass), C.c_int(shard_index), C.c_int(shard_count), _p(w), _p(rgba),
+           _p(pl) if pl is not None else None, C.c_uint64(0 if pl is None else len(pl)))
     assert rc == 0
     return w, rgba
 
@@ -113,3 +130,56 @@ def psnr(img, ref, peak=None):
     mse = np.mean((a - b) ** 2)
     peak = float(b.max()) if peak is None else peak
     return float("inf") if mse == 0 else 10.0 * np.log10(peak * peak / mse)
+
+
+def with_render_params(rec, **params):
+    """Re-issue a recorded scene's render parameters with extra / overriding keys (before its final setupRender)."""
+    i = max(k for k, l in enumerate(rec.lines) if l == "setupRender")
+    rec.lines.pop(i)
+    for k, v in params.items():
+        rec.lines = [l for l in rec.lines if not (l.split()[:2] == ["paramsSetInt", k] or l.split()[:2] == ["paramsSetFloat", k])]
+        if isinstance(v, bool):
+            rec.lines.append(f"paramsSetBool {k} {1 if v else 0}")
+        elif isinstance(v, int):
+            rec.lines.append(f"paramsSetInt {k} {v}")
+        elif isinstance(v, float):
+            rec.lines.append(f"paramsSetFloat {k} {v!r}")
+        else:
+            rec.lines.append(f"paramsSetString {k} {v}")
+    rec.lines.append("setupRender")
+    return rec
+
+
+def emu_adaptive_render(yi):
+    """TiledIntegrator::render's pass loop (the one Interface.render runs on the GPU) over the CPU emulation:
+    -> (image, resampled pixels per adaptive pass)."""
+    from libyafaray_b200 import interface
+
+    a = yi.assemble()
+    pr, rp = a["params"], yi.render_params
+    f32 = np.float32
+    film = emu_pt_render(a, n_samples=pr.aa_samples, offset=0, aa_pass=0)
+    threshold = f32(rp.get("AA_threshold", 0.05))
+    floor_pixels = int(np.floor(f32(f32(rp.get("AA_resampled_floor", 0.0)) * f32(pr.width * pr.height)) / f32(100.0)))
+    acum, mult, resampled, changed, hist = pr.aa_samples, f32(1.0), 0, True, []
+    for i in range(1, pr.aa_passes):
+        mult = f32(mult * f32(pr.aa_sample_multiplier_factor))
+        plist, skip = None, False
+        if resampled <= 0 and not changed:
+            skip = True
+        elif threshold > 0:
+            plist = emu_film_flags(a, film[0], film[1], yi.aa_noise_params(threshold))
+            resampled, changed = len(plist), False
+        else:
+            resampled, changed = pr.width * pr.height, False
+        hist.append(0 if skip else resampled)
+        n = int(np.ceil(f32(pr.aa_inc_samples) * mult))
+        if not skip and resampled > 0:
+            emu_pt_render(a, n_samples=n, offset=acum, aa_pass=i, pixel_list=plist, film=film)
+        acum += n
+        if resampled < floor_pixels:
+            ratio = min(f32(8.0), f32(floor_pixels) / f32(resampled)) if resampled > 0 else f32(8.0)
+            threshold = f32(threshold * f32(f32(1.0) - f32(0.1) * ratio))
+            if threshold > 0:
+                changed = True
+    return interface.normalize_film(film[0], film[1]), hist

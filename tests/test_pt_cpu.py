@@ -65,6 +65,29 @@ def test_stages_vs_live_reference_multi_pass_and_rr():
     assert helpers.psnr(img, ref) >= PSNR_MIN
 
 
+ADAPTIVE = [
+    dict(AA_passes=3, AA_inc_samples=2, AA_threshold=0.03),
+    dict(AA_passes=4, AA_inc_samples=1, AA_threshold=0.02, AA_resampled_floor=60.0, AA_detect_color_noise=True, AA_variance_pixels=4, AA_variance_edge_size=6,
+         AA_dark_detection_type="linear", AA_dark_threshold_factor=0.5, AA_sample_multiplier_factor=1.5),
+]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("aa", ADAPTIVE)
+def test_adaptive_aa_vs_live_reference(aa):
+    """ImageFilm::nextPass noise detection + the adaptive pass loop: same pixels flagged, same image as the reference."""
+    kw = dict(width=64, height=36, spp=2, bounces=3)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(helpers.with_render_params(rec, **aa))
+    yi = interface.Interface()
+    scenes_pt.cornell_box(yi, accelerator="yafaray-b200-bvh8", **kw)
+    yi.render_params.update(aa)
+    img, hist = helpers.emu_adaptive_render(yi)
+    assert any(0 < h < kw["width"] * kw["height"] for h in hist), hist      # the passes really were adaptive
+    assert helpers.psnr(img, ref) >= PSNR_MIN, (helpers.psnr(img, ref), hist)
+
+
 def test_interface_rejects_unsupported_features():
     yi = interface.Interface()
     yi.paramsSetString("type", "glass")

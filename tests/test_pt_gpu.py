@@ -94,3 +94,40 @@ def test_unsupported_scene_is_rejected_not_approximated():
     yi.cameras["cam"]["aperture"] = 0.1
     with pytest.raises(Y4Error):
         yi.render()
+
+
+ADAPTIVE = [
+    dict(AA_passes=3, AA_inc_samples=2, AA_threshold=0.03),
+    dict(AA_passes=4, AA_inc_samples=1, AA_threshold=0.02, AA_resampled_floor=60.0, AA_detect_color_noise=True, AA_variance_pixels=4, AA_variance_edge_size=6,
+         AA_dark_detection_type="linear", AA_dark_threshold_factor=0.5, AA_sample_multiplier_factor=1.5),
+]
+
+
+@pytest.mark.parametrize("aa", ADAPTIVE)
+def test_adaptive_aa_on_device_matches_the_cpu_emulation_and_the_reference(aa):
+    """y4gpu_pt_next_pass (ImageFilm::nextPass on the device) + Interface.render's adaptive pass loop."""
+    kw = dict(width=64, height=36, spp=2, bounces=3)
+    yi = _gpu(**kw)
+    yi.render_params.update(aa)
+    img = yi.render()
+    emu_img, hist = helpers.emu_adaptive_render(yi)
+    assert yi.resampled_per_pass == hist                       # the same number of pixels flagged in every pass
+    assert any(0 < h < kw["width"] * kw["height"] for h in hist)
+    assert helpers.psnr(img, emu_img) >= 100.0
+    if helpers.have_ref("ref_render"):
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        ref, _ = helpers.ref_render(helpers.with_render_params(rec, **aa))
+        assert helpers.psnr(img, ref) >= PSNR_MIN
+
+
+def test_next_pass_flags_every_unsampled_pixel_and_respects_the_threshold():
+    kw = dict(width=48, height=27, spp=1, bounces=2)
+    yi = _gpu(**kw)
+    yi.upload()
+    ptr, n = yi.next_pass(yi.aa_noise_params(0.05))            # empty film: weight 0 everywhere -> every pixel
+    assert n == 48 * 27
+    yi.render_pass(4, 0, 0)
+    _, n_lo = yi.next_pass(yi.aa_noise_params(1e-6))
+    _, n_hi = yi.next_pass(yi.aa_noise_params(1e6))
+    assert n_hi == 0 and 0 < n_lo <= 48 * 27
