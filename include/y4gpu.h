@@ -189,7 +189,11 @@ typedef struct y4gpu_pt_params
 	uint32_t rr_seed;             /* seed of the per-path Russian-roulette hash (the reference uses rand()) */
 	uint32_t wave_size;           /* pixel-samples processed per wavefront (0 = default 2^21) */
 	int32_t profile;              /* 1: time every kernel class with CUDA events and count BVH visits (slower; for the roofline) */
-	int32_t reserved[6];
+	int32_t transp_shadows;       /* integrator transpShad: shadow rays take the intersectTs rules (material visibility only,
+	                                 tmin <= t < t_max; accelerator_kdtree.cc:911-1061).  Every supported material is opaque,
+	                                 so a blocker always shadows and the filter colour is exactly 1 */
+	int32_t shadow_depth;         /* integrator shadowDepth (unused while every supported material is opaque) */
+	int32_t reserved[4];
 } y4gpu_pt_params;
 
 typedef struct y4gpu_pt_stats

@@ -64,7 +64,7 @@ class PtParams(C.Structure):
                 ("aa_pixelwidth", C.c_float), ("aa_clamp_samples", C.c_float), ("filter_type", C.c_int32),
                 ("shadow_bias_auto", C.c_int32), ("shadow_bias", C.c_float), ("min_raydist_auto", C.c_int32), ("min_raydist", C.c_float),
                 ("base_sampling_offset", C.c_uint32), ("rr_seed", C.c_uint32), ("wave_size", C.c_uint32), ("profile", C.c_int32),
-                ("reserved", C.c_int32 * 6)]  # fmt: skip
+                ("transp_shadows", C.c_int32), ("shadow_depth", C.c_int32), ("reserved", C.c_int32 * 4)]  # fmt: skip
 
 
 class PtStats(C.Structure):

@@ -236,7 +236,6 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	// ---- the supported set; everything else is rejected, never approximated ----
 	if(n_mat == 0) { ctx->err = "no materials"; return Y4GPU_ERR_ARG; }
 	if(n_light > Y4_PT_MAX_LIGHTS) { ctx->err = "more than 64 lights"; return Y4GPU_ERR_UNSUPPORTED; }
-	if(cam->aperture != 0.f) { ctx->err = "depth of field (aperture != 0) is not supported by the GPU back end"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(params->bounces < 1 || params->bounces > 11) { ctx->err = "bounces must be 1..11 (sample dimensions 4*depth+4 < 50)"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(params->path_samples < 1 || params->width < 1 || params->height < 1) { ctx->err = "bad path_samples / film size"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_mat; ++i)
@@ -506,6 +505,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	}
 	for(int l = 0; l < n_lanes; ++l) { const int rc = pt_alloc_wave(ctx, pt->lanes[l], wave_size); if(rc) return rc; }
 	const int trace_blocks = n_lanes > 1 ? pt->trace_blocks_shared : 0;
+	const int shadow_kind = pt->params.transp_shadows ? Y4_TRACE_TSHADOW : Y4_TRACE_SHADOW;
 	const int stage_minb = n_lanes > 1 && pt->stage_min_blocks < 3 ? 3 : pt->stage_min_blocks;
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass_number;
 	const Y4PtScene &dsc = sc;
@@ -574,7 +574,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
 		for(size_t j = 0; j < all_lk.size(); ++j)
 		{
-			Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
+			Y4_PT_TRACE(shadow_kind, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
 			if(j + 1 == all_lk.size()) break;          // the last sample is resolved by the start stage
 			Q.in_q = lane.q_hit0; Q.in_count = n_hit0; Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
 			a.all_lights = 1; a.l_prev = all_lk[j].first; a.k_prev = all_lk[j].second; a.l = all_lk[j + 1].first; a.k = all_lk[j + 1].second;
@@ -603,13 +603,13 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 				if(closing) break;
 				if(sc.n_lights)
 				{
-					Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
+					Y4_PT_TRACE(shadow_kind, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
 					for(int k = 1; k < max_ls; ++k)
 					{
 						Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
 						a.l_prev = -1; a.k_prev = k - 1; a.l = -1; a.k = k;
 						Y4_PT_LAUNCH(4, launch_stage<kStDirectStep>(stage_minb, grid, st, dsc, W, ps, a, Q));
-						Y4_PT_TRACE(Y4_TRACE_SHADOW, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
+						Y4_PT_TRACE(shadow_kind, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
 					}
 				}
 				cur ^= 1; n_cur = n_next;

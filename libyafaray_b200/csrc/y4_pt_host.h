@@ -45,6 +45,8 @@ inline Y4PtCamera derive_camera(const y4gpu_pt_camera &c)
 	o.pos = tov(position); o.vright = tov(vright); o.vup = tov(vup); o.vto = tov(vto);
 	o.near_p = tov(near_p); o.near_n = tov(cam_z); o.far_p = tov(far_p); o.far_n = tov(cam_z);
 	o.resx = c.resx; o.resy = c.resy;
+	o.aperture = c.aperture; o.dof_distance = c.dof_distance;
+	o.dof_rt = tov(c.aperture * cam_x); o.dof_up = tov(c.aperture * cam_y);       // setAxis: "premul with aperture"
 	return o;
 }
 

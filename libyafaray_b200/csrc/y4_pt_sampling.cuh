@@ -26,6 +26,7 @@
 #define Y4_PI ((Y4_WIDE) 3.14159265358979323846264338327950288L)
 #define Y4_2PI ((Y4_WIDE) 6.28318530717958647692528676655900577L)
 #define Y4_PI_2 ((Y4_WIDE) 1.57079632679489661923132169163975144L)
+#define Y4_PI_4 ((Y4_WIDE) 0.785398163397448309615660845819875721L)   /* math::div_pi_by_4 */
 #define Y4_1_PI ((Y4_WIDE) 0.31830988618379067153776752674502872L)
 #define Y4_1_2PI ((Y4_WIDE) 0.15915494309189533576888376337251L)
 #define Y4_4_PI ((Y4_WIDE) 1.2732395447351626861510701069801L)

@@ -95,14 +95,48 @@ Y4_HD Y4PixelSampling y4_pixel_sampling(const Y4PtScene &sc, const Y4PtPass &ps,
 	return r;
 }
 
-Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py)
+// Vec3::shirleyDisk (src/geometry/vector.cc:128-165): concentric square -> disk map; math::div_pi_by_4 is a long double
+// constant, so the angle is formed wide and rounded once; cos/sin are the FAST_TRIG approximations
+Y4_HD void y4_shirley_disk(float r_1, float r_2, float &u, float &v)
+{
+	float phi = 0.f, r = 0.f;
+	const float a = xsub(xmul(2.f, r_1), 1.f), b = xsub(xmul(2.f, r_2), 1.f);
+	if(a > -b)
+	{
+		if(a > b) { r = a; phi = (float) xdmul(Y4_PI_4, (Y4_WIDE) xdiv(b, a)); }
+		else { r = b; phi = (float) xdmul(Y4_PI_4, (Y4_WIDE) xsub(2.f, xdiv(a, b))); }
+	}
+	else
+	{
+		if(a < b) { r = -a; phi = (float) xdmul(Y4_PI_4, (Y4_WIDE) xadd(4.f, xdiv(b, a))); }
+		else
+		{
+			r = -b;
+			phi = b != 0.f ? (float) xdmul(Y4_PI_4, (Y4_WIDE) xsub(6.f, xdiv(a, b))) : 0.f;
+		}
+	}
+	u = xmul(r, y4_fast_cos(phi));
+	v = xmul(r, y4_fast_sin(phi));
+}
+
+// PerspectiveCamera::shootRay (camera_perspective.cc:128-146); lu, lv: lens sample (used when aperture != 0, disk bokeh)
+Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py, float lu, float lv)
 {
 	V3 d = xadd3(xadd3(xscale(cam.vright, px), xscale(cam.vup, py)), cam.vto);
 	d = xnormalize(d);
 	// Plane::rayIntersection: n * (p - from) / (dir * n)
 	const float tmin = xdiv(xdot(cam.near_n, xsub3(cam.near_p, cam.pos)), xdot(d, cam.near_n));
 	const float tmax = xdiv(xdot(cam.far_n, xsub3(cam.far_p, cam.pos)), xdot(d, cam.far_n));
-	return y4_mk_ray(cam.pos, tmin, d, tmax);
+	V3 from = cam.pos;
+	if(cam.aperture != 0.f)
+	{
+		float u, v;
+		y4_shirley_disk(lu, lv, u, v);
+		const V3 li = xadd3(xscale(cam.dof_rt, u), xscale(cam.dof_up, v));
+		from = xadd3(from, li);
+		d = xnormalize(xsub3(xscale(d, cam.dof_distance), li));
+	}
+	return y4_mk_ray(from, tmin, d, tmax);
 }
 
 // Elemental steps take the path's flag word in a register (`f`); the fused stage functions further
@@ -115,7 +149,15 @@ Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py)
 Y4_HD Y4Ray y4_primary_ray(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp)
 {
 	const Y4PixelSampling s = y4_pixel_sampling(sc, ps, pix, samp);
-	return y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy));
+	float lens_u = 0.5f, lens_v = 0.5f;
+	if(sc.cam.aperture != 0.f)
+	{
+		// renderTile: hal_u(3) / hal_v(5) are started per pixel at pass_offs + offset and advanced once per sample of the
+		// pass (integrator_tiled.cc:285-286,316-317,336-340); sample `samp` of the pass takes the (samp + 1)-th value
+		Y4Halton hu = y4_halton_start(3u, ps.pass_offs + s.offset), hv = y4_halton_start(5u, ps.pass_offs + s.offset);
+		for(uint32_t k = 0; k <= samp; ++k) { lens_u = y4_halton_next(hu); lens_v = y4_halton_next(hv); }
+	}
+	return y4_camera_ray(sc.cam, xadd((float) s.x, s.dx), xadd((float) s.y, s.dy), lens_u, lens_v);
 }
 Y4_HD void y4_pt_gen(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
 {

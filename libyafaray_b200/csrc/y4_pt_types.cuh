@@ -32,6 +32,9 @@ struct Y4PtCamera          // PerspectiveCamera state after ctor + setAxis (came
 	V3 pos, vright, vup, vto;
 	V3 near_p, near_n, far_p, far_n;
 	int resx, resy;
+	// depth of field (aperture != 0): lens offsets dof_rt * u + dof_up * v, focus at dof_distance (camera_perspective.cc:58-59,136-143)
+	V3 dof_rt, dof_up;
+	float aperture, dof_distance;
 };
 
 struct Y4PtMaterial

@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 	if(QUEUE) n = __ldg(queue_count);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t lt_mask = (1u << lane) - 1u;
-	const uint32_t vis_bit = KIND == Y4_TRACE_CLOSEST ? Y4_TRI_VIS_CLOSEST : Y4_TRI_VIS_SHADOW;
+	const uint32_t vis_bit = KIND == Y4_TRACE_CLOSEST ? Y4_TRI_VIS_CLOSEST : (KIND == Y4_TRACE_SHADOW ? Y4_TRI_VIS_SHADOW : Y4_TRI_VIS_TSHADOW);
 	uint2 stack[Y4_STACK_SIZE];
 	unsigned long long my_nodes = 0, my_tris = 0, my_live = 0;
 	bool have = false, exhausted = false;
@@ -256,6 +256,8 @@ int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_
 	int rc;
 	if(kind == Y4_TRACE_CLOSEST) rc = d_queue ? launch<Y4_TRACE_CLOSEST, true>(ctx, counted, a) : launch<Y4_TRACE_CLOSEST, false>(ctx, counted, a);
 	else if(kind == Y4_TRACE_SHADOW) rc = d_queue ? launch<Y4_TRACE_SHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_SHADOW, false>(ctx, counted, a);
+	// opaque-only transparent-shadow query of the path tracer: intersectTs ray range and visibility, first blocker ends the ray
+	else if(kind == Y4_TRACE_TSHADOW) rc = d_queue ? launch<Y4_TRACE_TSHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_TSHADOW, false>(ctx, counted, a);
 	else { ctx->err = "bad trace kind"; return Y4GPU_ERR_ARG; }
 	if(rc) return rc;
 	ctx->stats.kernel_launches++;

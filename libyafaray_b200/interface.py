@@ -118,6 +118,8 @@ class Interface:
         p = dict(self.params)
         if p.get("type") != "perspective":
             raise Y4Error(f"camera type '{p.get('type')}' is not supported by the GPU back end")
+        if float(p.get("aperture", 0.0)) != 0.0 and (p.get("bokeh_type", "disk1") != "disk1" or p.get("bokeh_bias", "uniform") != "uniform"):
+            raise Y4Error("depth of field is supported with the default lens only (bokeh_type=disk1, bokeh_bias=uniform)")
         self.cameras[name] = p
         return True
 
@@ -134,8 +136,8 @@ class Interface:
             raise Y4Error(f"integrator type '{p.get('type')}' is not supported by the GPU back end")
         if p.get("caustic_type", "path") in ("photon", "both"):
             raise Y4Error("photon caustics are not supported by the GPU back end")
-        if p.get("transpShad", False) or p.get("do_AO", False):
-            raise Y4Error("transparent shadows / AO in the path tracer are not supported by the GPU back end yet")
+        if p.get("do_AO", False):
+            raise Y4Error("ambient occlusion in the path tracer is not supported by the GPU back end")
         self.integrators[name] = p
         return True
 
@@ -331,6 +333,7 @@ class Interface:
         pr.bounces, pr.path_samples = int(integ.get("bounces", 3)), int(integ.get("path_samples", 32))
         pr.russian_roulette_min_bounces, pr.no_recursive = int(integ.get("russian_roulette_min_bounces", 0)), int(integ.get("no_recursive", False))
         pr.transp_background = int(integ.get("bg_transp", False))
+        pr.transp_shadows, pr.shadow_depth = int(bool(integ.get("transpShad", False))), int(integ.get("shadowDepth", 4))
         if bg is not None:
             c, pw = bg.get("color", (0.0, 0.0, 0.0, 1.0)), np.float32(bg.get("power", 1.0))
             pr.background[:] = [float(np.float32(c[k]) * pw) for k in range(3)]

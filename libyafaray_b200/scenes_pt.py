@@ -60,7 +60,7 @@ def _box(lo, hi, yaw_deg, centre):
 
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
-                oren_nayar=False, integrator="pathtracing"):
+                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
@@ -120,6 +120,9 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     api.paramsSetInt("resx", width)
     api.paramsSetInt("resy", height)
     api.paramsSetFloat("focal", 1.6 * height / width if width > height else 1.6)
+    if aperture:
+        api.paramsSetFloat("aperture", aperture)
+        api.paramsSetFloat("dof_distance", dof_distance)
     api.createCamera("cam")
 
     api.paramsClearAll()

@@ -27,8 +27,10 @@ static void trace(const Y4Bvh8 &bvh, int kind, const Y4Ray *rays, const uint32_t
 		uint2 stack[Y4_STACK_SIZE];
 		hits[i].t = 0.f; hits[i].bu = 0.f; hits[i].bv = 0.f; hits[i].prim = -1;
 		if(!(pr.t_hi > pr.t_lo)) continue;
+		uint32_t filt[16], filt_mat[16]; int n_filt = 0;
 		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray<Y4_TRACE_CLOSEST>(bvh, pr, hits[i], stack, nullptr, nullptr, nullptr, nullptr, 0);
-		else y4_trace_ray<Y4_TRACE_SHADOW>(bvh, pr, hits[i], stack, nullptr, nullptr, nullptr, nullptr, 0);
+		else if(kind == Y4_TRACE_SHADOW) y4_trace_ray<Y4_TRACE_SHADOW>(bvh, pr, hits[i], stack, nullptr, nullptr, nullptr, nullptr, 0);
+		else y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, hits[i], stack, nullptr, filt, filt_mat, &n_filt, 16);
 	}
 }
 
@@ -87,6 +89,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	W.ray = ray.data(); W.ray_next = ray2.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = &scontrib[0].x;
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
 	for(uint32_t i = 0; i < n; ++i) { pix[i] = pixel_list ? pixel_list[i / ns_local] : i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
+	const int shadow_kind = params->transp_shadows ? Y4_TRACE_TSHADOW : Y4_TRACE_SHADOW;
 	// same stage sequence as y4gpu_pt_render_pass (y4_pt.cu), queues as vectors
 	for(uint32_t i = 0; i < n; ++i) y4_pt_gen(sc, W, ps, i);
 	trace(bvh, Y4_TRACE_CLOSEST, W.ray, nullptr, n, W.hit);
@@ -97,7 +100,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	for(uint32_t i = 0; i < n; ++i) push(y4_stage_primary(sc, W, ps, i, all_lk.empty() ? -1 : all_lk[0].first), i, n, &q_hit0, &q_shadow);
 	for(size_t j = 0; j < all_lk.size(); ++j)
 	{
-		trace(bvh, Y4_TRACE_SHADOW, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
+		trace(bvh, shadow_kind, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
 		if(j + 1 == all_lk.size()) break;
 		q_shadow.clear();
 		for(uint32_t i : q_hit0) push(y4_stage_direct_step(sc, W, ps, i, true, all_lk[j].first, all_lk[j].second, all_lk[j + 1].first, all_lk[j + 1].second), i, n, nullptr, &q_shadow);
@@ -120,12 +123,12 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 			if(closing) break;
 			if(sc.n_lights)
 			{
-				trace(bvh, Y4_TRACE_SHADOW, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
+				trace(bvh, shadow_kind, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
 				for(int k = 1; k < max_ls; ++k)
 				{
 					q_shadow.clear();
 					for(uint32_t i : q_cur) push(y4_stage_direct_step(sc, W, ps, i, false, -1, k - 1, -1, k), i, n, nullptr, &q_shadow);
-					trace(bvh, Y4_TRACE_SHADOW, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
+					trace(bvh, shadow_kind, W.sray, q_shadow.data(), q_shadow.size(), W.shit);
 				}
 			}
 			q_cur.swap(q_next);

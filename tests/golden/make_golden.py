@@ -7,6 +7,7 @@ from /root/reference by `make -C oracle ref`).  Run in the build container only:
   rays_sphere.npz    <- oracle/_ref/ref_raybatch on scenes.displaced_sphere(40, 20): primary,
                         shadow and diffuse batches with the reference kd-tree's hit records
   rays_soup.npz      <- same on scenes.triangle_soup(3000) with incoherent + segment rays
+  pt_dof.npz         <- the same harness on the Cornell box with a lens (PT_GOLDEN_DOF)
   pt_city.npz        <- the same harness on scenes_pt.city (instanced buildings) for PT_GOLDEN_CITY
   pt_cornell.npz     <- oracle/_ref/ref_render (reference PathIntegrator + kd-tree through the C API,
                         threads=1, tiles linear) on scenes_pt.cornell_box for the PT_GOLDEN configurations
@@ -37,15 +38,26 @@ PT_GOLDEN_CITY = {
 }
 
 
-def make_city():
+# depth of field (aperture != 0: lens samples from Halton(3)/(5), Shirley disk) -> pt_dof.npz
+PT_GOLDEN_DOF = {
+    "dof_disk": dict(scene="cornell", width=64, height=36, spp=4, bounces=3, aperture=0.06, dof_distance=1.9),
+}
+
+
+def make_extra(configs, filename):
     from libyafaray_b200 import scenes_pt
 
     out = {}
-    for key, kw in PT_GOLDEN_CITY.items():
+    for key, kw in configs.items():
         rec = helpers.ScriptRecorder()
         scenes_pt.build(rec, **kw)
         out[key] = helpers.ref_render(rec)[0]
-    np.savez_compressed(os.path.join(HERE, "pt_city.npz"), **out)
+    np.savez_compressed(os.path.join(HERE, filename), **out)
+
+
+def make_city():
+    make_extra(PT_GOLDEN_CITY, "pt_city.npz")
+    make_extra(PT_GOLDEN_DOF, "pt_dof.npz")
 
 
 def main():

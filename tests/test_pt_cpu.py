@@ -14,9 +14,10 @@ from libyafaray_b200._lib import Y4Error
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 sys.path.insert(0, GOLD)
-from make_golden import PT_GOLDEN, PT_GOLDEN_CITY  # noqa: E402
+from make_golden import PT_GOLDEN, PT_GOLDEN_CITY, PT_GOLDEN_DOF  # noqa: E402
 
-ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: ("pt_city.npz", v) for k, v in PT_GOLDEN_CITY.items()}}
+ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: ("pt_city.npz", v) for k, v in PT_GOLDEN_CITY.items()},
+              **{k: ("pt_dof.npz", v) for k, v in PT_GOLDEN_DOF.items()}}
 
 PSNR_MIN = 50.0  # BASELINE.json: PSNR >= 50 dB vs the reference at equal spp with identical sample sequences
 
@@ -88,6 +89,22 @@ def test_adaptive_aa_vs_live_reference(aa):
     assert helpers.psnr(img, ref) >= PSNR_MIN, (helpers.psnr(img, ref), hist)
 
 
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+def test_transparent_shadow_mode_vs_live_reference():
+    """integrator transpShad=true: shadow rays take the intersectTs ray range / visibility rules (all supported materials are opaque)."""
+    kw = dict(width=64, height=36, spp=4, bounces=3)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    i = [k for k, l in enumerate(rec.lines) if l.startswith("createIntegrator")][0]
+    rec.lines[i:i] = ["paramsSetBool transpShad 1", "paramsSetInt shadowDepth 3"]
+    ref, _ = helpers.ref_render(rec)
+    yi = interface.Interface()
+    scenes_pt.cornell_box(yi, accelerator="yafaray-b200-bvh8", **kw)
+    yi.integrators["pt"]["transpShad"] = True
+    w, rgba = helpers.emu_pt_render(yi.assemble())
+    assert helpers.psnr(interface.normalize_film(w, rgba), ref) >= 100.0
+
+
 def test_interface_rejects_unsupported_features():
     yi = interface.Interface()
     yi.paramsSetString("type", "glass")
@@ -98,6 +115,12 @@ def test_interface_rejects_unsupported_features():
     yi.paramsSetFloat("transparency", 0.5)
     with pytest.raises(Y4Error):
         yi.createMaterial("t")
+    yi.paramsClearAll()
+    yi.paramsSetString("type", "perspective")
+    yi.paramsSetFloat("aperture", 0.1)
+    yi.paramsSetString("bokeh_type", "hexagon")
+    with pytest.raises(Y4Error):
+        yi.createCamera("c")
     yi.paramsClearAll()
     yi.paramsSetString("type", "spherelight")
     with pytest.raises(Y4Error):

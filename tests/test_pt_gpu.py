@@ -13,9 +13,10 @@ from libyafaray_b200 import interface, scenes_pt
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 sys.path.insert(0, GOLD)
-from make_golden import PT_GOLDEN, PT_GOLDEN_CITY  # noqa: E402
+from make_golden import PT_GOLDEN, PT_GOLDEN_CITY, PT_GOLDEN_DOF  # noqa: E402
 
-ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: ("pt_city.npz", v) for k, v in PT_GOLDEN_CITY.items()}}
+ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: ("pt_city.npz", v) for k, v in PT_GOLDEN_CITY.items()},
+              **{k: ("pt_dof.npz", v) for k, v in PT_GOLDEN_DOF.items()}}
 
 PSNR_MIN = 50.0  # BASELINE.json north_star: PSNR >= 50 dB at equal spp with identical sample sequences
 
@@ -91,7 +92,7 @@ def test_adaptive_pixel_list_and_offsets():
 def test_unsupported_scene_is_rejected_not_approximated():
     from libyafaray_b200._lib import Y4Error
     yi = _gpu(width=32, height=18, spp=1, bounces=3)
-    yi.cameras["cam"]["aperture"] = 0.1
+    yi.integrators["pt"]["bounces"] = 12        # sample dimensions 4 * depth + 4 would leave the reference's 50-dimension tables
     with pytest.raises(Y4Error):
         yi.render()
 
@@ -131,3 +132,12 @@ def test_next_pass_flags_every_unsampled_pixel_and_respects_the_threshold():
     _, n_lo = yi.next_pass(yi.aa_noise_params(1e-6))
     _, n_hi = yi.next_pass(yi.aa_noise_params(1e6))
     assert n_hi == 0 and 0 < n_lo <= 48 * 27
+
+
+def test_transparent_shadow_mode_and_dof_match_the_cpu_emulation():
+    kw = dict(width=64, height=36, spp=3, bounces=3, aperture=0.08, dof_distance=1.8)
+    yi = _gpu(**kw)
+    yi.integrators["pt"]["transpShad"] = True
+    img = yi.render()
+    w, rgba = helpers.emu_pt_render(yi._assembled)
+    assert helpers.psnr(img, interface.normalize_film(w, rgba)) >= 100.0
