@@ -174,7 +174,8 @@ enum { Y4GPU_FILTER_BOX = 0, Y4GPU_FILTER_GAUSS = 1, Y4GPU_FILTER_MITCHELL = 2, 
 typedef struct y4gpu_pt_params
 {
 	/* integrator (integrator_path_tracer.cc:292-366) */
-	int32_t bounces, path_samples, russian_roulette_min_bounces, no_recursive;
+	int32_t bounces, path_samples, russian_roulette_min_bounces, no_recursive;   /* path_samples == 0: direct lighting only
+	                                 (DirectLightIntegrator::integrate, integrator_direct_light.cc:94-143: emission + every light) */
 	int32_t transp_background;
 	float background[3];          /* constant background colour * power */
 	/* render parameters (scene.cc:528-644, imagefilm.cc:45-127) */

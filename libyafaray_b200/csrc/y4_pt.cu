@@ -237,7 +237,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	if(n_mat == 0) { ctx->err = "no materials"; return Y4GPU_ERR_ARG; }
 	if(n_light > Y4_PT_MAX_LIGHTS) { ctx->err = "more than 64 lights"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(params->bounces < 1 || params->bounces > 11) { ctx->err = "bounces must be 1..11 (sample dimensions 4*depth+4 < 50)"; return Y4GPU_ERR_UNSUPPORTED; }
-	if(params->path_samples < 1 || params->width < 1 || params->height < 1) { ctx->err = "bad path_samples / film size"; return Y4GPU_ERR_ARG; }
+	if(params->path_samples < 0 || params->width < 1 || params->height < 1) { ctx->err = "bad path_samples / film size"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_mat; ++i)
 		if(mats[i].type != Y4GPU_MAT_SHINYDIFFUSE && mats[i].type != Y4GPU_MAT_LIGHT) { ctx->err = "unsupported material type"; return Y4GPU_ERR_UNSUPPORTED; }
 	for(uint32_t i = 0; i < n_light; ++i)
@@ -579,6 +579,13 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 			Q.in_q = lane.q_hit0; Q.in_count = n_hit0; Q.out_q = nullptr; Q.out_count = nullptr; Q.sh_count = new_queue_count(1);
 			a.all_lights = 1; a.l_prev = all_lk[j].first; a.k_prev = all_lk[j].second; a.l = all_lk[j + 1].first; a.k = all_lk[j + 1].second;
 			Y4_PT_LAUNCH(4, launch_stage<kStDirectStep>(stage_minb, grid, st, dsc, W, ps, a, Q));
+		}
+		if(sc.n_paths == 0 && !all_lk.empty())
+		{
+			// direct lighting only (DirectLightIntegrator): just fold the last light sample into the pixel colour
+			Q.in_q = lane.q_hit0; Q.in_count = n_hit0; Q.out_q = lane.q_path[0]; Q.out_count = new_queue_count(-1); Q.sh_q = lane.q_shadow; Q.sh_count = nullptr;
+			a.all_lights = 1; a.sub = 0; a.l_prev = all_lk.back().first; a.k_prev = all_lk.back().second;
+			Y4_PT_LAUNCH(3, launch_stage<kStStart>(stage_minb, grid, st, dsc, W, ps, a, Q));
 		}
 		Y4Ray *const ray_buf[2] = {lane.wave.ray, lane.wave.ray_next};
 		for(int sub = 0; sub < sc.n_paths; ++sub)

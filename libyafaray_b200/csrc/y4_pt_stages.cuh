@@ -199,7 +199,7 @@ Y4_HD bool y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uin
 	f = Y4_PF_HIT0;
 	if(vx.m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
 	const uint32_t path_flags = sc.no_recursive ? (uint32_t) Y4_BSDF_ALL : (uint32_t) Y4_BSDF_DIFFUSE;
-	if(vx.m.bsdf_flags & path_flags) f |= Y4_PF_PATHS;
+	if(sc.n_paths > 0 && (vx.m.bsdf_flags & path_flags)) f |= Y4_PF_PATHS;       // n_paths == 0: DirectLightIntegrator (integrator_direct_light.cc:94-143)
 	return true;
 }
 

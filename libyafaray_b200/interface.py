@@ -132,8 +132,10 @@ class Interface:
 
     def createIntegrator(self, name):
         p = dict(self.params)
-        if p.get("type") != "pathtracing":
+        if p.get("type") not in ("pathtracing", "directlighting"):
             raise Y4Error(f"integrator type '{p.get('type')}' is not supported by the GPU back end")
+        if p.get("caustics", False):
+            raise Y4Error("photon caustics are not supported by the GPU back end")
         if p.get("caustic_type", "path") in ("photon", "both"):
             raise Y4Error("photon caustics are not supported by the GPU back end")
         if p.get("do_AO", False):
@@ -331,6 +333,8 @@ class Interface:
 
         pr = _lib.PtParams()
         pr.bounces, pr.path_samples = int(integ.get("bounces", 3)), int(integ.get("path_samples", 32))
+        if integ.get("type") == "directlighting":      # same kernels, no path loop
+            pr.bounces, pr.path_samples = 1, 0
         pr.russian_roulette_min_bounces, pr.no_recursive = int(integ.get("russian_roulette_min_bounces", 0)), int(integ.get("no_recursive", False))
         pr.transp_background = int(integ.get("bg_transp", False))
         pr.transp_shadows, pr.shadow_depth = int(bool(integ.get("transpShad", False))), int(integ.get("shadowDepth", 4))

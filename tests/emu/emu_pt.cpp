@@ -105,6 +105,8 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		q_shadow.clear();
 		for(uint32_t i : q_hit0) push(y4_stage_direct_step(sc, W, ps, i, true, all_lk[j].first, all_lk[j].second, all_lk[j + 1].first, all_lk[j + 1].second), i, n, nullptr, &q_shadow);
 	}
+	if(sc.n_paths == 0 && !all_lk.empty())
+		for(uint32_t i : q_hit0) y4_stage_start(sc, W, ps, i, all_lk.back().first, all_lk.back().second, 0);
 	Y4Ray *const ray_buf[2] = {ray.data(), ray2.data()};
 	for(int sub = 0; sub < sc.n_paths; ++sub)
 	{
