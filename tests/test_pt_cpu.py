@@ -126,7 +126,7 @@ def test_interface_rejects_unsupported_features():
     with pytest.raises(Y4Error):
         yi.createLight("l")
     yi.paramsClearAll()
-    yi.paramsSetString("type", "directlighting")
+    yi.paramsSetString("type", "photonmapping")
     with pytest.raises(Y4Error):
         yi.createIntegrator("i")
     yi.paramsClearAll()
