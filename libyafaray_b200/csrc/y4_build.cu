@@ -203,6 +203,13 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 		ctx->stats.kernel_launches++;
 		if(++levels > 256) { ctx->err = "collapse did not terminate"; return Y4GPU_ERR_CUDA; }
 	}
+	// the traversal kernels keep at most one pending sibling group per level (+ a few postponed triangle groups, which are
+	// bounded separately) on a Y4_STACK_SIZE-entry stack: refuse a tree they could overflow instead of corrupting memory
+	if(levels > Y4_STACK_SIZE - 8)
+	{
+		ctx->err = "BVH8 is deeper than the traversal stack (degenerate input: very many coincident triangles)";
+		return Y4GPU_ERR_UNSUPPORTED;
+	}
 	uint32_t fin[2];
 	Y4_CUDA(ctx, cudaMemcpyAsync(fin, counters.p, sizeof(fin), cudaMemcpyDeviceToHost, st));
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, st));

@@ -104,28 +104,33 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 			else if(STAGE == kStStart) push = y4_stage_start(sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
 			else push = y4_stage_path(sc, W, ps, i, a.depth, a.sub, a.k_prev);
 		}
-		if(STAGE == kStPrimary || STAGE == kStDirectStep || STAGE == kStPath)
+		// queue appends: one atomic per warp; when a stage feeds both queues their two 32-bit lengths share one 64-bit
+		// counter slot (path count low, shadow count high) and a single 64-bit atomic reserves both ranges
+		const uint32_t m0 = (STAGE != kStStart) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_S0) : 0u;
+		const uint32_t m1 = (STAGE != kStStart) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_S1) : 0u;
+		const uint32_t mp = (STAGE != kStDirectStep) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH) : 0u;
+		if(m0 | m1 | mp)
 		{
-			const uint32_t m0 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S0), m1 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S1);
-			if(m0 | m1)
+			const uint32_t n_sh = (uint32_t) (__popc(m0) + __popc(m1)), n_p = (uint32_t) __popc(mp);
+			uint32_t at_sh = 0u, at_p = 0u;
+			if(lane == 0)
 			{
-				uint32_t at = 0u;
-				if(lane == 0) at = atomicAdd(Q.sh_count, (uint32_t) (__popc(m0) + __popc(m1)));
-				at = __shfl_sync(0xffffffffu, at, 0);
-				if(push & Y4_PUSH_S0) Q.sh_q[at + __popc(m0 & lt_mask)] = i;
-				if(push & Y4_PUSH_S1) Q.sh_q[at + __popc(m0) + __popc(m1 & lt_mask)] = W.n + i;
+				if((STAGE == kStPrimary || STAGE == kStPath) && Q.sh_count == Q.out_count + 1)
+				{
+					const unsigned long long old = atomicAdd(reinterpret_cast<unsigned long long *>(Q.out_count), ((unsigned long long) n_sh << 32) | n_p);
+					at_p = (uint32_t) old; at_sh = (uint32_t) (old >> 32);
+				}
+				else
+				{
+					if(n_sh) at_sh = atomicAdd(Q.sh_count, n_sh);
+					if(n_p) at_p = atomicAdd(Q.out_count, n_p);
+				}
 			}
-		}
-		if(STAGE == kStPrimary || STAGE == kStStart || STAGE == kStPath)
-		{
-			const uint32_t mp = __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH);
-			if(mp)
-			{
-				uint32_t at = 0u;
-				if(lane == 0) at = atomicAdd(Q.out_count, (uint32_t) __popc(mp));
-				at = __shfl_sync(0xffffffffu, at, 0);
-				if(push & Y4_PUSH_PATH) Q.out_q[at + __popc(mp & lt_mask)] = i;
-			}
+			at_sh = __shfl_sync(0xffffffffu, at_sh, 0);
+			at_p = __shfl_sync(0xffffffffu, at_p, 0);
+			if(push & Y4_PUSH_S0) Q.sh_q[at_sh + __popc(m0 & lt_mask)] = i;
+			if(push & Y4_PUSH_S1) Q.sh_q[at_sh + __popc(m0) + __popc(m1 & lt_mask)] = W.n + i;
+			if(push & Y4_PUSH_PATH) Q.out_q[at_p + __popc(mp & lt_mask)] = i;
 		}
 	}
 }
@@ -430,7 +435,11 @@ int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out)
 		{
 			// queue lengths of the pass (copied to pinned memory before ev1): rays actually traced
 			uint64_t sum[4] = {0, 0, 0, 0};
-			for(const auto &ck : pt->counter_kinds) sum[ck.second & 3] += (uint32_t) pt->h_counters[ck.first];
+			for(const auto &ck : pt->counter_kinds)
+			{
+				const unsigned long long v = pt->h_counters[ck.first & 0x7fffffffu];
+				sum[ck.second & 3] += (ck.first >> 31) ? (uint32_t) (v >> 32) : (uint32_t) v;
+			}
 			pt->stats.rays_closest = pt->dense_closest + sum[0]; pt->stats.rays_shadow = sum[1];
 			pt->stats.camera_hits = sum[2]; pt->stats.path_entries = sum[0] + sum[3];
 			if(pt->params.profile)
@@ -529,6 +538,14 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	pt->counter_kinds.clear(); pt->dense_closest = 0;
 	size_t next_slot = 8;
 	auto new_slot = [&]() -> unsigned long long * { return pt->d_counters + (next_slot < need ? next_slot++ : need - 1); };
+	// a path queue and a shadow queue filled by the same stage: adjacent halves of one 64-bit slot
+	auto new_queue_pair = [&](int kind_path, int kind_shadow, uint32_t *&path_count, uint32_t *&shadow_count)
+	{
+		if(kind_path >= 0) pt->counter_kinds.push_back(std::make_pair((uint32_t) next_slot, kind_path));
+		if(kind_shadow >= 0) pt->counter_kinds.push_back(std::make_pair((uint32_t) next_slot | 0x80000000u, kind_shadow));
+		path_count = reinterpret_cast<uint32_t *>(new_slot());
+		shadow_count = path_count + 1;
+	};
 	auto new_queue_count = [&](int kind) -> uint32_t *
 	{
 		if(kind >= 0) pt->counter_kinds.push_back(std::make_pair((uint32_t) next_slot, kind));
@@ -568,8 +585,9 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		// camera rays -> closest hits -> camera-hit stage with the first light sample
 		Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, ns_local, shard_index, shard_count));
 		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, nullptr, nullptr); pt->dense_closest += W.n;
-		uint32_t *n_hit0 = new_queue_count(2);
-		Q.out_q = lane.q_hit0; Q.out_count = n_hit0; Q.sh_q = lane.q_shadow; Q.sh_count = new_queue_count(1);
+		uint32_t *n_hit0 = nullptr;
+		new_queue_pair(2, 1, n_hit0, Q.sh_count);
+		Q.out_q = lane.q_hit0; Q.out_count = n_hit0; Q.sh_q = lane.q_shadow;
 		a.l = all_lk.empty() ? -1 : all_lk[0].first;
 		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
 		for(size_t j = 0; j < all_lk.size(); ++j)
@@ -602,9 +620,10 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 				if(closing && !sc.n_lights) break;                       // nothing waits to be folded in
 				W.ray = ray_buf[depth & 1]; W.ray_next = ray_buf[(depth + 1) & 1];
 				if(!closing) Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, lane.q_path[cur], n_cur);
-				uint32_t *n_next = new_queue_count(depth + 1 < sc.bounces ? 0 : (closing ? -1 : 3));
+				uint32_t *n_next = nullptr;
+				new_queue_pair(depth + 1 < sc.bounces ? 0 : (closing ? -1 : 3), sc.n_lights && !closing ? 1 : -1, n_next, Q.sh_count);
 				Q.in_q = lane.q_path[cur]; Q.in_count = n_cur; Q.out_q = lane.q_path[cur ^ 1]; Q.out_count = n_next;
-				Q.sh_q = lane.q_shadow; Q.sh_count = new_queue_count(sc.n_lights && !closing ? 1 : -1);
+				Q.sh_q = lane.q_shadow;
 				a.all_lights = 0; a.depth = depth; a.sub = sub; a.l_prev = -1; a.k_prev = sc.n_lights ? max_ls - 1 : -1;
 				Y4_PT_LAUNCH(3, launch_stage<kStPath>(stage_minb, grid, st, dsc, W, ps, a, Q));
 				if(closing) break;
