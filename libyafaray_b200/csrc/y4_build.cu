@@ -52,11 +52,11 @@ __global__ void __launch_bounds__(256) k_tri_boxes(const float *__restrict__ ver
 }
 
 // 2. Morton keys
-__global__ void __launch_bounds__(256) k_morton(const Y4Box *__restrict__ tb, int n, Y4Box scene, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+__global__ void __launch_bounds__(256) k_morton(const Y4Box *__restrict__ tb, int n, Y4Box scene, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals, int sized)
 {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if(i >= n) return;
-	keys[i] = y4_morton63(tb[i], scene);
+	keys[i] = sized ? y4_morton63_sized(tb[i], scene) : y4_morton63(tb[i], scene);
 	vals[i] = (uint32_t) i;
 }
 
@@ -159,7 +159,7 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 		ctx->bound[3 + a] = (float) ((double) ctx->raw_bound[3 + a] + foo);
 	}
 
-	k_morton<<<grid_n, tpb, 0, st>>>(tb.p, n, scene, keys_a.p, vals_a.p);
+	k_morton<<<grid_n, tpb, 0, st>>>(tb.p, n, scene, keys_a.p, vals_a.p, ctx->morton_sized);
 	cub::DoubleBuffer<uint64_t> dk(keys_a.p, keys_b.p);
 	cub::DoubleBuffer<uint32_t> dv(vals_a.p, vals_b.p);
 	size_t tmp_bytes = 0;

@@ -66,6 +66,32 @@ Y4_HD uint64_t y4_morton63(const Y4Box &tri, const Y4Box &scene)
 	return (y4_expand21(qx) << 2) | (y4_expand21(qy) << 1) | y4_expand21(qz);
 }
 
+// Extended Morton key (Vinkler et al. 2017): one bit of the primitive's SIZE after every xyz triple, so that a triangle
+// much larger than its neighbours leaves their subtree at the octree level whose cells are about its own size instead
+// of inflating every box down to a deep leaf.  15 levels of [x y z s] + one more xyz triple = 63 bits.  Scenes of
+// uniformly small triangles have all-zero size bits and keep plain Morton order (at 16 instead of 21 bits per axis).
+Y4_HD uint64_t y4_morton63_sized(const Y4Box &tri, const Y4Box &scene)
+{
+	const float ex = scene.hix - scene.lox, ey = scene.hiy - scene.loy, ez = scene.hiz - scene.loz;
+	const float cx = 0.5f * (tri.lox + tri.hix), cy = 0.5f * (tri.loy + tri.hiy), cz = 0.5f * (tri.loz + tri.hiz);
+	float nx = ex > 0.f ? (cx - scene.lox) / ex : 0.f;
+	float ny = ey > 0.f ? (cy - scene.loy) / ey : 0.f;
+	float nz = ez > 0.f ? (cz - scene.loz) / ez : 0.f;
+	nx = fminf(fmaxf(nx, 0.f), 1.f); ny = fminf(fmaxf(ny, 0.f), 1.f); nz = fminf(fmaxf(nz, 0.f), 1.f);
+	const uint32_t qx = (uint32_t) fminf(nx * 65536.f, 65535.f), qy = (uint32_t) fminf(ny * 65536.f, 65535.f), qz = (uint32_t) fminf(nz * 65536.f, 65535.f);
+	// size relative to the cells of each level, per axis (the normalisation above is per axis too): the largest relative extent
+	float sx = ex > 0.f ? (tri.hix - tri.lox) / ex : 0.f, sy = ey > 0.f ? (tri.hiy - tri.loy) / ey : 0.f, sz = ez > 0.f ? (tri.hiz - tri.loz) / ez : 0.f;
+	const float sn = fminf(fmaxf(fmaxf(sx, sy), sz), 1.f);
+	const uint32_t qs = (uint32_t) fminf(sn * 32768.f, 32767.f);
+	uint64_t key = 0;
+	for(int l = 0; l < 15; ++l)
+	{
+		key = (key << 4) | (uint64_t) ((((qx >> (15 - l)) & 1u) << 3) | (((qy >> (15 - l)) & 1u) << 2) | (((qz >> (15 - l)) & 1u) << 1) | ((qs >> (14 - l)) & 1u));
+	}
+	key = (key << 3) | (uint64_t) (((qx & 1u) << 2) | ((qy & 1u) << 1) | (qz & 1u));
+	return key;
+}
+
 Y4_HD int y4_clz64(uint64_t x)
 {
 #if defined(__CUDA_ARCH__)

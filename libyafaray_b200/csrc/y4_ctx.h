@@ -43,6 +43,7 @@ struct y4gpu_ctx
 
 	// warp scheduling knobs of k_trace (env Y4GPU_FETCH_THRESHOLD / Y4GPU_POSTPONE_DIV override)
 	int fetch_threshold = 20, postpone_div = 5, min_blocks = 3;
+	int morton_sized = 1;      // extended Morton keys with size bits (env Y4GPU_MORTON_SIZED=0: plain 21-bit-per-axis keys)
 
 	y4gpu_stats stats = {};
 	Y4Pt *pt = nullptr;

@@ -24,7 +24,7 @@ void emu_build(const float *verts, const uint32_t *flags, int n, int leaf_max, E
 	Y4Box scene = y4_box_empty();
 	for(int i = 0; i < n; ++i) { tb[i] = y4_tri_box(verts + 9ull * i); scene = y4_box_union(scene, tb[i]); }
 	std::vector<std::pair<uint64_t, uint32_t>> kv(n);
-	for(int i = 0; i < n; ++i) kv[i] = {y4_morton63(tb[i], scene), (uint32_t) i};
+	for(int i = 0; i < n; ++i) kv[i] = {y4_morton63_sized(tb[i], scene), (uint32_t) i};
 	std::stable_sort(kv.begin(), kv.end(), [](const std::pair<uint64_t, uint32_t> &a, const std::pair<uint64_t, uint32_t> &b) { return a.first < b.first; });
 	std::vector<uint64_t> keys(n);
 	std::vector<uint32_t> sorted_prim(n);
