@@ -68,3 +68,70 @@ def test_edge_cases():
         exp = helpers.emu_brute(tris, rays, 0)
         assert np.array_equal(got["prim"], exp["prim"]) and np.array_equal(got["t"], exp["t"])
         assert (acc.intersect(rays[:0])["prim"].shape[0]) == 0
+
+
+def test_soup_golden_on_gpu():
+    """Committed hit records of the reference kd-tree on a random triangle soup (incoherent closest + segment any-hit)."""
+    import os
+    d = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rays_soup.npz"))
+    from libyafaray_b200.accelerator import AcceleratorB200
+    tris = scenes.triangle_soup(int(d["scene"][0]))
+    acc = AcceleratorB200(tris)
+    r = helpers.compare_closest(acc.intersect(d["incoherent"]), d["hit_incoherent"])
+    assert r["bad"] == 0 and r["t_out_of_tol"] == 0 and r["uv_out_of_tol"] == 0 and r["bit_exact_t"] == r["n_hit_both"], r
+    assert np.array_equal(acc.isShadowed(d["segment"])["prim"] >= 0, d["hit_segment"]["prim"] != -1)
+
+
+def test_degenerate_inputs_and_ray_ranges():
+    from libyafaray_b200.accelerator import AcceleratorB200
+    one = np.array([[-1, -1, 0, 1, -1, 0, 0, 1, 0]], np.float32)
+    # zero-area and duplicated triangles, axis-parallel rays (zero direction components)
+    tris = np.concatenate([one, one, np.zeros((3, 9), np.float32), one + np.float32(2)])
+    ax = np.zeros((6, 8), np.float32)
+    ax[:, 0:3] = [0.0, -0.5, 5.0]
+    ax[:, 7] = -1
+    ax[:, 4:7] = [[0, 0, -1], [0, 0, 1], [1, 0, 0], [0, 1, 0], [-1, 0, 0], [0, -1, 0]]
+    acc = AcceleratorB200(tris)
+    got, exp = acc.intersect(ax), helpers.emu_brute(tris, ax, 0)
+    assert np.array_equal(got["t"], exp["t"]) and got["prim"][0] == 0 and (got["prim"][1:] == -1).all()   # exact tie: lowest primitive index
+    # visibility matrix + wrapper ranges (closest: tmin inclusive, tmax exclusive; shadow: advanced origin, t_max = tmax - 2 tmin)
+    tris = np.concatenate([one, one - np.array([0, 0, 1] * 3, np.float32)])
+    flags = np.array([2, 1 | 2 | 4], np.uint32)
+    acc = AcceleratorB200(tris, flags=flags)
+    ray = np.array([[0, -0.5, 5, 0, 0, 0, -1, -1]], np.float32)
+    assert acc.intersect(ray)["prim"][0] == 1 and acc.intersect(ray)["t"][0] == 6.0
+    acc = AcceleratorB200(tris)
+    r2 = np.array([[0, -0.5, 5, 5.0, 0, 0, -1, 6.0], [0, -0.5, 5, 5.5, 0, 0, -1, 6.0], [0, -0.5, 5, 6.0, 0, 0, -1, -1], [0, -0.5, 5, 7.0, 0, 0, -1, 6.5]], np.float32)
+    assert list(acc.intersect(r2)["prim"]) == [0, -1, 1, -1]
+    r3 = np.array([[0, -0.5, 5, 1.0, 0, 0, -1, 5.5], [0, -0.5, 5, 1.0, 0, 0, -1, 6.5]], np.float32)
+    assert list(acc.isShadowed(r3)["prim"] >= 0) == [False, True]
+    # rays that can hit nothing must come back as misses, not hang: NaN / infinite origins, zero direction
+    bad = np.array([[np.nan, 0, 5, 0, 0, 0, -1, -1], [np.inf, 0, 5, 0, 0, 0, -1, -1], [0, -0.5, 5, 0, 0, 0, 0, -1], [0, -0.5, 5, 0, np.nan, 0, -1, -1]], np.float32)
+    assert (acc.intersect(bad)["prim"] == -1).all() and (acc.isShadowed(bad)["prim"] == -1).all()
+
+
+def test_transparent_shadows_and_device_resident_batches(sphere):
+    import torch
+    tris, acc = sphere
+    prim = scenes.primary_rays(96, 96)
+    h = acc.intersect(prim)
+    p, nrm, ok = scenes.hit_points_normals(tris, prim, h["t"], h["prim"])
+    sh = scenes.shadow_rays(p, ok)
+    # all-opaque materials: intersectTs reports "shadowed" exactly where it finds a blocker in [tmin, t_max) with material visibility
+    ts = acc.isShadowedTransparent(sh, 4, np.ones((1, 3), np.float32))
+    adv = sh.copy()
+    adv[:, 0:3] += sh[:, 4:7] * sh[:, 3:4]
+    adv[:, 7] = sh[:, 7] - 2 * sh[:, 3]
+    exp = acc.intersect(adv)                                    # closest hit of the advanced ray with the same [tmin, t_max) interval
+    assert np.array_equal(ts["prim"] >= 0, exp["prim"] >= 0)
+    # device tensors in, device tensors out, on the caller's stream
+    s = torch.cuda.Stream()
+    acc.set_stream(s.cuda_stream)
+    with torch.cuda.stream(s):
+        d_rays = torch.from_numpy(prim).cuda()
+        d_out = torch.empty((len(prim), 4), dtype=torch.float32, device="cuda")
+        acc.intersect(d_rays, d_out)
+    s.synchronize()
+    acc.set_stream(0)
+    got = d_out.cpu().numpy()
+    assert np.array_equal(got[:, 0], h["t"]) and np.array_equal(got[:, 3].view(np.int32), h["prim"])
