@@ -31,6 +31,7 @@ Y4_HD float xsqrt(float a) { return __fsqrt_rn(a); }
 Y4_HD double xdmul(double a, double b) { return __dmul_rn(a, b); }
 Y4_HD double xdadd(double a, double b) { return __dadd_rn(a, b); }
 Y4_HD double xdsub(double a, double b) { return __dsub_rn(a, b); }
+Y4_HD double xddiv(double a, double b) { return __ddiv_rn(a, b); }
 #else
 // host build: compiled with -ffp-contract=off (see tests/emu/Makefile)
 Y4_HD float xmul(float a, float b) { return a * b; }
@@ -41,6 +42,7 @@ Y4_HD float xsqrt(float a) { return sqrtf(a); }
 Y4_HD double xdmul(double a, double b) { return a * b; }
 Y4_HD double xdadd(double a, double b) { return a + b; }
 Y4_HD double xdsub(double a, double b) { return a - b; }
+Y4_HD double xddiv(double a, double b) { return a / b; }
 #endif
 
 #if !defined(__CUDACC__)

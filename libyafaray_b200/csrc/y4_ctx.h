@@ -43,7 +43,8 @@ struct y4gpu_ctx
 
 	// warp scheduling knobs of k_trace (env Y4GPU_FETCH_THRESHOLD / Y4GPU_POSTPONE_DIV override)
 	int fetch_threshold = 20, postpone_div = 5, min_blocks = 3;
-	int morton_sized = 1;      // extended Morton keys with size bits (env Y4GPU_MORTON_SIZED=0: plain 21-bit-per-axis keys)
+	int morton_sized = -1;     // key order: -1 build both binary trees, keep the smaller surface-area sum; 0 plain 21-bit-per-axis Morton keys; 1 extended keys with size bits (env Y4GPU_MORTON_SIZED)
+	int morton_used = 0;       // what the last build chose
 
 	y4gpu_stats stats = {};
 	Y4Pt *pt = nullptr;

@@ -83,16 +83,39 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 	return o;
 }
 
-// PointLight ctor (light_point.cc:29-36), AreaLight ctor (light_area.cc:33-52)
+// PointLight ctor (light_point.cc:29-36), AreaLight ctor (light_area.cc:33-52), and the three lights below
 inline Y4PtLight derive_light(const y4gpu_pt_light &l)
 {
 	Y4PtLight o;
 	memset(&o, 0, sizeof(o));
 	o.type = l.type; o.samples = l.samples; o.cast_shadows = l.cast_shadows;
 	o.pos = v3(l.from[0], l.from[1], l.from[2]);
-	if(l.type == Y4GPU_LIGHT_POINT)
+	o.color = c3(l.power * l.color[0], l.power * l.color[1], l.power * l.color[2]);       // color_ = col * inte
+	if(l.type == Y4GPU_LIGHT_POINT) return o;
+	if(l.type == Y4GPU_LIGHT_DIRECTIONAL)                 // DirectionalLight ctor (light_directional.cc:28-39); init() only feeds photon code
 	{
-		o.color = c3(l.power * l.color[0], l.power * l.color[1], l.power * l.color[2]);
+		o.dir = tov(normalized(hv(l.point1)));
+		o.radius = l.radius; o.infinite = l.infinite;
+		return o;
+	}
+	if(l.type == Y4GPU_LIGHT_SUN)                         // SunLight ctor (light_sun.cc:29-43)
+	{
+		o.dir = tov(normalized(hv(l.point1)));
+		y4_coords_system(tov(hv(l.point1)), o.du, o.dv);  // createCoordsSystem(dir): the ctor argument, not the normalised member
+		float angle = l.angle;
+		if(angle > 80.f) angle = 80.f;
+		o.cos_angle = y4_fast_cos((float) ((long double) angle * 0.01745329251994329576923690768489L));
+		o.invpdf = (float) (6.283185307179586476925286766559L * (long double) (1.f - o.cos_angle));
+		o.pdf = (float) (1.0 / (double) o.invpdf);
+		o.pdf = fminf(o.pdf, sqrtf(3.402823466e+38f));
+		o.color = c3(o.color.r * o.pdf, o.color.g * o.pdf, o.color.b * o.pdf);            // col_pdf_
+		return o;
+	}
+	if(l.type == Y4GPU_LIGHT_SPHERE)                      // SphereLight ctor (light_sphere.cc:30-40)
+	{
+		o.radius = l.radius;
+		o.sq_radius = l.radius * l.radius;
+		o.sq_radius_eps = (float) ((double) o.sq_radius * 1.000003815);
 		return o;
 	}
 	const HV corner = hv(l.from), to_x = hv(l.point1) - corner, to_y = hv(l.point2) - corner;

@@ -1,6 +1,6 @@
 // Per-vertex shading logic of the wavefront path tracer: surface set-up, the supported
 // materials (shinydiffusemat without mirror/transparency/translucency/nodes, light_mat), the
-// supported lights (pointlight, arealight) and one direct-light sample with MIS.  Restated from
+// supported lights (pointlight, arealight, directional, sunlight, spherelight) and one direct-light sample with MIS.  Restated from
 // the reference operation for operation (never-contracted fp32, see y4_common.cuh):
 //   TrianglePrimitive::getSurface              src/geometry/primitive/primitive_triangle.cc:97-176
 //   ShinyDiffuseMaterial::sample/eval/pdf/emit src/material/material_shiny_diffuse.cc:197-385
@@ -8,6 +8,9 @@
 //   LightMaterial::sample/emit                 src/material/material_simple.cc:41-58
 //   PointLight::illuminate                     src/light/light_point.cc:38-57
 //   AreaLight::illumSample/intersect           src/light/light_area.cc:66-96,117-151
+//   DirectionalLight::illuminate               src/light/light_directional.cc:58-80
+//   SunLight::illumSample/intersect            src/light/light_sun.cc:54-78
+//   SphereLight::illumSample/sphereIntersect   src/light/light_sphere.cc:55-98
 //   MonteCarloIntegrator::diracLight / areaLightSampleLight / areaLightSampleMaterial
 //                                              src/integrator/surface/integrator_montecarlo.cc:80-383
 #pragma once
@@ -152,6 +155,149 @@ Y4_HD Y4Ray y4_mk_ray(const V3 o, float tmin, const V3 d, float tmax)
 	Y4Ray r; r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tmin = tmin; r.dx = d.x; r.dy = d.y; r.dz = d.z; r.tmax = tmax; return r;
 }
 
+// ---- lights ----------------------------------------------------------------------------------------
+// LSample / light_ray fields the integrator reads back from Light::illuminate / illumSample
+struct Y4LSample { V3 dir; float tmax, pdf; C3 col; };
+
+// sample::cone (include/sampler/sample.h:80-86)
+Y4_HD V3 y4_sample_cone(const V3 d, const V3 u, const V3 v, float max_cos_ang, float s1, float s2)
+{
+	const float cos_ang = xsub(1.f, xmul(xsub(1.f, max_cos_ang), s2));
+	const float sin_ang = xsqrt(xsub(1.f, xmul(cos_ang, cos_ang)));
+	const float t1 = (float) (Y4_2PI * (Y4_WIDE) s1);
+	const V3 a = xadd3(xscale(u, y4_fast_cos(t1)), xscale(v, y4_fast_sin(t1)));
+	return xadd3(xscale(a, sin_ang), xscale(d, cos_ang));
+}
+
+// SphereLight::sphereIntersect (light_sphere.cc:55-67): float members, double literals promote the discriminant and the quotients
+Y4_HD bool y4_sphere_intersect(const V3 from, const V3 dir, const V3 c, float r2, float &d1, float &d2)
+{
+	const V3 vf = xsub3(from, c);
+	const float ea = xdot(dir, dir);
+	const float eb = xdot(xscale(vf, 2.f), dir);
+	const float ec = xsub(xdot(vf, vf), r2);
+	float osc = (float) xdsub((double) xmul(eb, eb), xdmul(xdmul(4.0, (double) ea), (double) ec));
+	if(osc < 0.f) { d1 = xsqrt(xdiv(ec, ea)); return false; }
+	osc = xsqrt(osc);
+	const double den = xdmul(2.0, (double) ea);
+	d1 = (float) xddiv((double) xsub(-eb, osc), den);
+	d2 = (float) xddiv((double) xadd(-eb, osc), den);
+	return true;
+}
+
+// Light::illuminate of the dirac lights: PointLight (light_point.cc:38-57), DirectionalLight (light_directional.cc:58-80)
+Y4_HD bool y4_light_illuminate(const Y4PtLight &L, const V3 p, Y4LSample &ls)
+{
+	ls.pdf = 1.f;
+	if(L.type == Y4GPU_LIGHT_POINT)
+	{
+		V3 ldir = xsub3(L.pos, p);
+		const float dist_sqr = xadd(xadd(xmul(ldir.x, ldir.x), xmul(ldir.y, ldir.y)), xmul(ldir.z, ldir.z));
+		const float dist = xsqrt(dist_sqr);
+		if(dist == 0.f) return false;
+		const float idist_sqr = xdiv(1.f, dist_sqr);
+		ls.dir = xscale(ldir, xdiv(1.f, dist));
+		ls.tmax = dist;
+		ls.col = cscale(L.color, idist_sqr);
+		return true;
+	}
+	// directional
+	if(!L.infinite)
+	{
+		const V3 vec = xsub3(L.pos, p);
+		const float dist = xlen(xcross(L.dir, vec));          // distance from the cylinder axis
+		if(dist > L.radius) return false;
+		ls.tmax = xdot(vec, L.dir);
+		if(ls.tmax <= 0.f) return false;
+	}
+	else ls.tmax = -1.f;
+	ls.dir = L.dir;
+	ls.col = L.color;
+	return true;
+}
+
+// Light::illumSample of the sampled lights: AreaLight (light_area.cc:66-96), SunLight (light_sun.cc:54-68),
+// SphereLight (light_sphere.cc:69-98)
+Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, float s2, Y4LSample &ls)
+{
+	if(L.type == Y4GPU_LIGHT_AREA)
+	{
+		const V3 p = xadd3(xadd3(L.pos, xscale(L.to_x, s1)), xscale(L.to_y, s2));
+		V3 ldir = xsub3(p, from);
+		const float dist_sqr = xdot(ldir, ldir);
+		const float dist = xsqrt(dist_sqr);
+		if(dist <= 0.f) return false;
+		ldir = xscale(ldir, xdiv(1.f, dist));
+		const float cos_angle = xdot(ldir, L.fnormal);
+		if(cos_angle <= 0.f) return false;
+		// dist_sqr * math::num_pi / (area_ * cos_angle): num_pi is long double -> wide product and quotient, one rounding to float
+		ls.pdf = (float) (xdmul((Y4_WIDE) dist_sqr, Y4_PI) / (Y4_WIDE) xmul(L.area, cos_angle));
+		ls.dir = ldir; ls.tmax = dist; ls.col = L.color;
+		return true;
+	}
+	if(L.type == Y4GPU_LIGHT_SUN)
+	{
+		ls.dir = y4_sample_cone(L.dir, L.du, L.dv, L.cos_angle, s1, s2);
+		ls.tmax = -1.f; ls.col = L.color; ls.pdf = L.pdf;
+		return true;
+	}
+	// sphere
+	V3 cdir = xsub3(L.pos, from);
+	const float dist_sqr = xdot(cdir, cdir);
+	if(dist_sqr <= L.sq_radius) return false;                 // only emits on the outside
+	const float dist = xsqrt(dist_sqr);
+	const float idist_sqr = xdiv(1.f, dist_sqr);
+	const float cos_alpha = xsqrt(xsub(1.f, xmul(L.sq_radius, idist_sqr)));
+	cdir = xscale(cdir, xdiv(1.f, dist));
+	V3 cu, cv;
+	y4_coords_system(cdir, cu, cv);
+	ls.dir = y4_sample_cone(cdir, cu, cv, cos_alpha, s1, s2);
+	float d1, d2;
+	if(!y4_sphere_intersect(from, ls.dir, L.pos, L.sq_radius_eps, d1, d2)) return false;
+	ls.tmax = d1;
+	ls.pdf = xdiv(1.f, xmul(2.f, xsub(1.f, cos_alpha)));
+	ls.col = L.color;
+	return true;
+}
+
+// Light::intersect of the lights with canIntersect(): AreaLight (light_area.cc:117-151), SunLight (light_sun.cc:70-78)
+Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, float &t, C3 &col, float &ipdf)
+{
+	if(L.type == Y4GPU_LIGHT_SUN)
+	{
+		const float cosine = xdot(dir, L.dir);
+		if(cosine < L.cos_angle) return false;
+		col = L.color; t = -1.f; ipdf = L.invpdf;
+		return true;
+	}
+	const float cos_angle = xdot(dir, L.fnormal);
+	if(cos_angle <= 0.f) return false;
+	bool hit = false;
+	// triIntersect(corner, c2, c3) then (corner, c3, c4), light_area.cc:117-134 (ray.from_ == sp.p, no tmin)
+	for(int k = 0; k < 2 && !hit; ++k)
+	{
+		const V3 a = L.pos, b = k ? L.c3 : L.c2, c = k ? L.c4 : L.c3;
+		const V3 e1 = xsub3(b, a), e2 = xsub3(c, a);
+		const V3 pvec = xcross(dir, e2);
+		const float det = xdot(e1, pvec);
+		if(det == 0.f) continue;
+		const float inv_det = xdiv(1.f, det);
+		const V3 tvec = xsub3(from, a);
+		const float u = xmul(xdot(tvec, pvec), inv_det);
+		if(u < 0.f || u > 1.f) continue;
+		const V3 qvec = xcross(tvec, e1);
+		const float v = xmul(xdot(dir, qvec), inv_det);
+		if((v < 0.f) || (xadd(u, v) > 1.f)) continue;
+		t = xmul(xdot(e2, qvec), inv_det);
+		hit = true;
+	}
+	if(!hit || !(t > 1.0e-10f)) return false;
+	// 1.f / (t * t) * area_ * cos_angle * math::div_1_by_pi (last factor long double)
+	ipdf = (float) xdmul((Y4_WIDE) xmul(xmul(xdiv(1.f, xmul(t, t)), L.area), cos_angle), Y4_1_PI);
+	col = L.color;
+	return true;
+}
+
 Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo,
                             float s1, float s2, Y4DirectOut &out)
 {
@@ -160,101 +306,55 @@ Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtM
 	out.ray[0] = out.ray[1] = y4_null_ray();
 	const float plen = xlen(sp.p);
 	const float tmin_shadow = sc.shadow_bias_auto ? xmul(sc.shadow_bias, fmaxf(1.f, plen)) : sc.shadow_bias;
-	if(L.type == Y4GPU_LIGHT_POINT)
+	Y4LSample ls;
+	if(y4_light_dirac(L.type))
 	{
-		// PointLight::illuminate + MonteCarloIntegrator::diracLight
-		V3 ldir = xsub3(L.pos, sp.p);
-		const float dist_sqr = xadd(xadd(xmul(ldir.x, ldir.x), xmul(ldir.y, ldir.y)), xmul(ldir.z, ldir.z));
-		const float dist = xsqrt(dist_sqr);
-		if(dist == 0.f) return;
-		const float idist_sqr = xdiv(1.f, dist_sqr);
-		ldir = xscale(ldir, xdiv(1.f, dist));
-		const C3 lcol = cscale(L.color, idist_sqr);
-		const float angle = m.flat_material ? 1.f : fabsf(xdot(sp.n, ldir));
-		const C3 surf = y4_mat_eval(m, sp, wo, ldir);
-		out.contrib[0] = cscale(cscale(cmul(surf, lcol), angle), 1.f);      // surf_col * lcol * angle * transmit_col(1)
-		out.ray[0] = y4_mk_ray(sp.p, tmin_shadow, ldir, dist);
+		// MonteCarloIntegrator::diracLight
+		if(!y4_light_illuminate(L, sp.p, ls)) return;
+		const float angle = m.flat_material ? 1.f : fabsf(xdot(sp.n, ls.dir));
+		const C3 surf = y4_mat_eval(m, sp, wo, ls.dir);
+		out.contrib[0] = cscale(cscale(cmul(surf, ls.col), angle), 1.f);    // surf_col * lcol * angle * transmit_col(1)
+		out.ray[0] = y4_mk_ray(sp.p, tmin_shadow, ls.dir, ls.tmax);
 		out.valid[0] = true;
 		return;
 	}
-	// ---- AreaLight::illumSample + areaLightSampleLight ----
+	const bool can_intersect = y4_light_can_intersect(L.type);
+	// ---- areaLightSampleLight ----
+	if(y4_light_illum_sample(L, sp.p, s1, s2, ls) && ls.pdf > 1e-6f)
 	{
-		const V3 p = xadd3(xadd3(L.pos, xscale(L.to_x, s1)), xscale(L.to_y, s2));
-		V3 ldir = xsub3(p, sp.p);
-		const float dist_sqr = xdot(ldir, ldir);
-		const float dist = xsqrt(dist_sqr);
-		if(dist > 0.f)
+		const C3 surf = y4_mat_eval(m, sp, wo, ls.dir);
+		const float angle = m.flat_material ? 1.f : fabsf(xdot(sp.n, ls.dir));
+		float w = 1.f;
+		if(can_intersect)
 		{
-			ldir = xscale(ldir, xdiv(1.f, dist));
-			const float cos_angle = xdot(ldir, L.fnormal);
-			if(cos_angle > 0.f)
+			const float m_pdf = y4_mat_pdf(m, sp, wo, ls.dir);
+			if(m_pdf > 1e-6f)
 			{
-				// dist_sqr * math::num_pi / (area_ * cos_angle): num_pi is long double -> wide product and quotient, one rounding to float
-				const float ls_pdf = (float) (xdmul((Y4_WIDE) dist_sqr, Y4_PI) / (Y4_WIDE) xmul(L.area, cos_angle));
-				if(ls_pdf > 1e-6f)
-				{
-					const C3 surf = y4_mat_eval(m, sp, wo, ldir);
-					const float angle = m.flat_material ? 1.f : fabsf(xdot(sp.n, ldir));
-					float w = 1.f;
-					const float m_pdf = y4_mat_pdf(m, sp, wo, ldir);
-					if(m_pdf > 1e-6f)
-					{
-						const float l2 = xmul(ls_pdf, ls_pdf), m2 = xmul(m_pdf, m_pdf);
-						w = xdiv(l2, xadd(l2, m2));
-					}
-					out.contrib[0] = cdiv(cscale(cscale(cmul(surf, L.color), angle), w), ls_pdf);
-					out.ray[0] = y4_mk_ray(sp.p, tmin_shadow, ldir, dist);
-					out.valid[0] = true;
-				}
+				const float l2 = xmul(ls.pdf, ls.pdf), m2 = xmul(m_pdf, m_pdf);
+				w = xdiv(l2, xadd(l2, m2));
 			}
 		}
+		out.contrib[0] = cdiv(cscale(cscale(cmul(surf, ls.col), angle), w), ls.pdf);
+		out.ray[0] = y4_mk_ray(sp.p, tmin_shadow, ls.dir, ls.tmax);
+		out.valid[0] = true;
 	}
-	// ---- areaLightSampleMaterial + AreaLight::intersect ----
+	// ---- areaLightSampleMaterial (lights with canIntersect() only) ----
+	if(can_intersect)
 	{
 		const float tmin_b = sc.ray_min_dist_auto ? xmul(sc.ray_min_dist, fmaxf(1.f, plen)) : sc.ray_min_dist;
 		V3 wi = v3(0.f, 0.f, 0.f);
 		float W = 0.f, s_pdf = 0.f; bool sampled;
 		const uint32_t fl = Y4_BSDF_GLOSSY | Y4_BSDF_DIFFUSE | Y4_BSDF_DISPERSIVE | Y4_BSDF_REFLECT | Y4_BSDF_TRANSMIT;
 		const C3 surf = y4_mat_sample(m, sp, wo, s1, s2, fl, wi, W, s_pdf, sampled);
-		if(s_pdf > 1e-6f)
+		float t = 0.f, ipdf = 0.f; C3 lcol = c3f(0.f);
+		if(s_pdf > 1e-6f && y4_light_intersect(L, sp.p, wi, t, lcol, ipdf) && ipdf > 1e-6f)
 		{
-			const float cos_angle = xdot(wi, L.fnormal);
-			if(cos_angle > 0.f)
-			{
-				float t = 0.f; bool hit = false;
-				// triIntersect(corner, c2, c3) then (corner, c3, c4), light_area.cc:117-134 (ray.from_ == sp.p, no tmin)
-				for(int k = 0; k < 2 && !hit; ++k)
-				{
-					const V3 a = L.pos, b = k ? L.c3 : L.c2, c = k ? L.c4 : L.c3;
-					const V3 e1 = xsub3(b, a), e2 = xsub3(c, a);
-					const V3 pvec = xcross(wi, e2);
-					const float det = xdot(e1, pvec);
-					if(det == 0.f) continue;
-					const float inv_det = xdiv(1.f, det);
-					const V3 tvec = xsub3(sp.p, a);
-					const float u = xmul(xdot(tvec, pvec), inv_det);
-					if(u < 0.f || u > 1.f) continue;
-					const V3 qvec = xcross(tvec, e1);
-					const float v = xmul(xdot(wi, qvec), inv_det);
-					if((v < 0.f) || (xadd(u, v) > 1.f)) continue;
-					t = xmul(xdot(e2, qvec), inv_det);
-					hit = true;
-				}
-				if(hit && t > 1.0e-10f)
-				{
-					// 1.f / (t * t) * area_ * cos_angle * math::div_1_by_pi (last factor long double)
-					const float ipdf = (float) xdmul((Y4_WIDE) xmul(xmul(xdiv(1.f, xmul(t, t)), L.area), cos_angle), Y4_1_PI);
-					if(ipdf > 1e-6f)
-					{
-						const float l_pdf = xdiv(1.f, ipdf);
-						const float l2 = xmul(l_pdf, l_pdf), m2 = xmul(s_pdf, s_pdf);
-						const float w = xdiv(m2, xadd(l2, m2));
-						out.contrib[1] = cscale(cscale(cmul(surf, L.color), w), W);
-						out.ray[1] = y4_mk_ray(sp.p, tmin_b, wi, t);
-						out.valid[1] = true;
-					}
-				}
-			}
+			const float l_pdf = xdiv(1.f, ipdf);
+			const float l2 = xmul(l_pdf, l_pdf), m2 = xmul(s_pdf, s_pdf);
+			const float w = xdiv(m2, xadd(l2, m2));
+			out.contrib[1] = cscale(cscale(cmul(surf, lcol), w), W);
+			out.ray[1] = y4_mk_ray(sp.p, tmin_b, wi, t);
+			out.valid[1] = true;
 		}
 	}
 }

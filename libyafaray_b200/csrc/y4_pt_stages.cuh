@@ -206,7 +206,7 @@ Y4_HD bool y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uin
 // number of samples doLightEstimation takes from light L (integrator_montecarlo.cc:396)
 Y4_HD int y4_light_num_samples(const Y4PtScene &sc, const Y4PtLight &L)
 {
-	if(L.type == Y4GPU_LIGHT_POINT) return 1;
+	if(y4_light_dirac(L.type)) return 1;
 	return (int) ceilf(xmul((float) L.samples, sc.aa_light_sample_multiplier));
 }
 
@@ -246,7 +246,7 @@ Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return 0u;
 	const Y4PtLight &L = sc.lights[l];
 	float s1 = 0.f, s2 = 0.f;
-	if(L.type != Y4GPU_LIGHT_POINT) y4_light_sample_numbers(sc, W, ps, i, l, k, num_samples, cache, s1, s2);
+	if(!y4_light_dirac(L.type)) y4_light_sample_numbers(sc, W, ps, i, l, k, num_samples, cache, s1, s2);
 	Y4DirectOut out;
 	y4_direct_sample(sc, L, vx.m, vx.sp, vx.wo, s1, s2, out);
 	const bool cast = L.cast_shadows && vx.m.receive_shadows;
@@ -286,7 +286,7 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 	if(k < num_samples - 1) { st3(W.acc_a, i, a); st3(W.acc_b, i, b); return; }
 	// last sample of this light: doLightEstimation's result
 	C3 dl = c3f(0.f);
-	if(L.type == Y4GPU_LIGHT_POINT) dl = cadd(dl, a);
+	if(y4_light_dirac(L.type)) dl = cadd(dl, a);
 	else
 	{
 		const float inv = xdiv(1.f, (float) num_samples);
@@ -354,6 +354,11 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 	const Y4PtMaterial &m = vx.m;
 	emit = c3f(0.f);
 	bool direct;
+#ifdef Y4_TEST_LIGHT_CHOICE_HOOK
+	// tests/emu only: every estimateOneDirectLight call of the reference advances its counter, also the ones this
+	// function skips because they evaluate to exactly zero (non-diffuse vertex) or that Russian roulette discards later
+	if(sc.n_lights > 1 && (depth == 0 || (f & Y4_PF_DIFF1))) y4_test_light_choice_called(pix, samp, sub, depth);
+#endif
 	if(depth == 0)
 	{
 		if(m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIFF1; else f &= ~(uint32_t) Y4_PF_DIFF1;
@@ -380,7 +385,10 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 	// With one light every draw picks light 0 (min(int(h * 1), 0)): nothing to compute or store.
 	if(sc.n_lights > 1)
 	{
-		const uint32_t corr = (pix * 1009u + ps.pass_offs + samp) * (uint32_t) (sc.bounces * sc.n_paths) + (uint32_t) (sub * sc.bounces + depth);
+		uint32_t corr = (pix * 1009u + ps.pass_offs + samp) * (uint32_t) (sc.bounces * sc.n_paths) + (uint32_t) (sub * sc.bounces + depth);
+#ifdef Y4_TEST_LIGHT_CHOICE_HOOK
+		corr = y4_test_light_choice(pix, samp, sub, depth, corr);   // tests/emu only: replays the reference's single-thread call counter
+#endif
 		const int lnum = (int) xmul(y4_halton2_at(sc.base_sampling_offset + corr - 1u, 1u), (float) sc.n_lights);
 		W.lnum[i] = (uint32_t) (lnum < sc.n_lights - 1 ? lnum : sc.n_lights - 1);
 	}

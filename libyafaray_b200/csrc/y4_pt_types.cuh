@@ -53,11 +53,19 @@ struct Y4PtLight
 {
 	int type;                   // Y4GPU_LIGHT_*
 	int samples, cast_shadows;
-	C3 color;                   // point: col*inte ; area: col*inte*pi
-	V3 pos;                     // point position / area corner
+	C3 color;                   // point, directional, sphere: col*inte ; area: col*inte*pi ; sun: col_pdf_ = col*inte*pdf_
+	V3 pos;                     // point position / area corner / sphere centre / finite directional position
 	V3 to_x, to_y, fnormal, normal, c2, c3, c4;
 	float area, inv_area;
+	// directional (light_directional.cc:28-39), sun (light_sun.cc:29-43), sphere (light_sphere.cc:30-40)
+	V3 dir, du, dv;             // normalised direction towards the light; sun: frame of the *unnormalised* ctor argument
+	float cos_angle, pdf, invpdf;
+	float radius, sq_radius, sq_radius_eps;
+	int infinite;
 };
+// Light::diracLight() / Light::canIntersect() of the supported lights (include/light/light_*.h)
+Y4_HD bool y4_light_dirac(int type) { return type == Y4GPU_LIGHT_POINT || type == Y4GPU_LIGHT_DIRECTIONAL; }
+Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN; }
 
 #define Y4_PT_MAX_LIGHTS 64
 #define Y4_FILTER_TABLE 16

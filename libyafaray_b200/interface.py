@@ -109,7 +109,7 @@ class Interface:
 
     def createLight(self, name):
         p = dict(self.params)
-        if p.get("type") not in ("pointlight", "arealight"):
+        if p.get("type") not in ("pointlight", "arealight", "directional", "sunlight", "spherelight"):
             raise Y4Error(f"light type '{p.get('type')}' is not supported by the GPU back end")
         self.lights[name] = p
         return True
@@ -324,6 +324,19 @@ class Interface:
             l.power, l.cast_shadows = float(p.get("power", 1.0)), int(p.get("cast_shadows", True))
             if p["type"] == "pointlight":
                 l.type = _lib.LIGHT_POINT
+                l.from_[:] = p.get("from", (0.0, 0.0, 0.0))
+            elif p["type"] == "directional":       # DirectionalLight::factory (light_directional.cc:116-157)
+                l.type, l.infinite = _lib.LIGHT_DIRECTIONAL, int(bool(p.get("infinite", True)))
+                l.point1[:] = p.get("direction", (0.0, 0.0, 1.0))
+                l.radius = 1.0
+                if not l.infinite:
+                    l.from_[:] = p.get("from", p.get("position", (0.0, 0.0, 0.0)))
+                    l.radius = float(p.get("radius", 1.0))
+            elif p["type"] == "sunlight":          # SunLight::factory (light_sun.cc:97-128)
+                l.type, l.samples, l.angle = _lib.LIGHT_SUN, int(p.get("samples", 4)), float(p.get("angle", 0.27))
+                l.point1[:] = p.get("direction", (0.0, 0.0, 1.0))
+            elif p["type"] == "spherelight":       # SphereLight::factory (light_sphere.cc:160-195)
+                l.type, l.samples, l.radius = _lib.LIGHT_SPHERE, int(p.get("samples", 4)), float(p.get("radius", 1.0))
                 l.from_[:] = p.get("from", (0.0, 0.0, 0.0))
             else:
                 l.type, l.samples = _lib.LIGHT_AREA, int(p.get("samples", 4))

@@ -60,8 +60,9 @@ def _box(lo, hi, yaw_deg, centre):
 
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
-                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0):
-    """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes."""
+                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=()):
+    """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
+    extra_lights: any of "sun", "directional", "directional_finite", "sphere" shining in through the open front."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
     _material(api, "white", white, **extra)
@@ -111,6 +112,38 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         api.paramsSetInt("samples", light_samples)
         api.paramsSetString("object_name", "h_lamp")
     api.createLight("lamp")
+    for kind in extra_lights:
+        api.paramsClearAll()
+        if kind == "sun":                               # wide cone so that several samples differ visibly
+            api.paramsSetString("type", "sunlight")
+            api.paramsSetVector("direction", 0.35, 0.55, -1.0)
+            api.paramsSetColor("color", 1.0, 0.95, 0.8, 1.0)
+            api.paramsSetFloat("power", 0.9)
+            api.paramsSetFloat("angle", 4.0)
+            api.paramsSetInt("samples", light_samples)
+        elif kind == "directional":
+            api.paramsSetString("type", "directional")
+            api.paramsSetVector("direction", -0.6, 0.25, -1.0)
+            api.paramsSetColor("color", 0.6, 0.7, 1.0, 1.0)
+            api.paramsSetFloat("power", 0.5)
+        elif kind == "directional_finite":              # a beam of radius 0.22 through the front opening
+            api.paramsSetString("type", "directional")
+            api.paramsSetVector("direction", 0.1, 0.4, -1.0)
+            api.paramsSetBool("infinite", False)
+            api.paramsSetVector("from", 0.45, 0.9, -1.2)
+            api.paramsSetFloat("radius", 0.22)
+            api.paramsSetColor("color", 1.0, 0.4, 0.3, 1.0)
+            api.paramsSetFloat("power", 1.5)
+        elif kind == "sphere":
+            api.paramsSetString("type", "spherelight")
+            api.paramsSetVector("from", 0.2, 0.75, 0.3)
+            api.paramsSetFloat("radius", 0.06)
+            api.paramsSetColor("color", 0.5, 1.0, 0.6, 1.0)
+            api.paramsSetFloat("power", 9.0)
+            api.paramsSetInt("samples", light_samples)
+        else:
+            raise ValueError(kind)
+        api.createLight("x_" + kind)
 
     api.paramsClearAll()
     api.paramsSetString("type", "perspective")

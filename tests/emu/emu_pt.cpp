@@ -2,6 +2,40 @@
 // (libyafaray_b200/csrc/y4_pt_stages.cuh) as serial loops on the CPU, with the emulated BVH8
 // traversal, so the stage logic can be checked against the reference renderer where no GPU exists.
 // Never linked into liby4gpu.so.
+#include <cstdint>
+#include <map>
+#include <tuple>
+#include <algorithm>
+#include <vector>
+// estimateOneDirectLight picks its light from Halton(2) at a per-thread call counter (integrator_montecarlo.cc:74-76,
+// integrator_tiled.cc:169-171).  With threads=1 and linear tiles that counter is a function of the render order, which
+// the emulation can replay (mode 1 records which vertices ask, emu_light_choice_finalize numbers them in the reference's
+// tile / pixel / sample / sub-path / depth order, mode 2 feeds the numbers back).  The product keeps its per-vertex index.
+#define Y4_TEST_LIGHT_CHOICE_HOOK 1
+typedef std::tuple<uint32_t, uint32_t, int, int> LcKey;      // pixel, sample, sub-path, depth
+static int g_lc_mode = 0;
+static std::map<LcKey, uint32_t> g_lc;
+static void y4_test_light_choice_called(uint32_t pix, uint32_t samp, int sub, int depth) { if(g_lc_mode == 1) g_lc[LcKey(pix, samp, sub, depth)] = 0u; }
+static uint32_t y4_test_light_choice(uint32_t pix, uint32_t samp, int sub, int depth, uint32_t corr)
+{
+	if(g_lc_mode == 2) { auto it = g_lc.find(LcKey(pix, samp, sub, depth)); return it == g_lc.end() ? corr : it->second; }
+	return corr;
+}
+extern "C" void emu_light_choice_mode(int mode) { g_lc_mode = mode; if(mode == 1) g_lc.clear(); }
+extern "C" uint64_t emu_light_choice_finalize(int width, int tile)
+{
+	typedef std::tuple<int, int, int, int, uint32_t, int, int> OrdKey;    // tile row, tile col, y, x, sample, sub, depth
+	std::vector<std::pair<OrdKey, LcKey>> order;
+	for(auto &kv : g_lc)
+	{
+		const int x = (int) (std::get<0>(kv.first) % (uint32_t) width), y = (int) (std::get<0>(kv.first) / (uint32_t) width);
+		order.push_back(std::make_pair(OrdKey(y / tile, x / tile, y, x, std::get<1>(kv.first), std::get<2>(kv.first), std::get<3>(kv.first)), kv.first));
+	}
+	std::sort(order.begin(), order.end());
+	uint32_t counter = 0;
+	for(auto &o : order) g_lc[o.second] = counter++;
+	return counter;
+}
 #include "../../libyafaray_b200/csrc/y4_trace.cuh"
 #include "../../libyafaray_b200/csrc/y4_pt_host.h"
 #include "../../libyafaray_b200/csrc/y4_faure.h"

@@ -8,6 +8,7 @@ from /root/reference by `make -C oracle ref`).  Run in the build container only:
                         shadow and diffuse batches with the reference kd-tree's hit records
   rays_soup.npz      <- same on scenes.triangle_soup(3000) with incoherent + segment rays
   pt_dof.npz         <- the same harness on the Cornell box with a lens (PT_GOLDEN_DOF)
+  pt_lights.npz      <- the same harness on the Cornell box with directional / sun / sphere lights (PT_GOLDEN_LIGHTS)
   pt_city.npz        <- the same harness on scenes_pt.city (instanced buildings) for PT_GOLDEN_CITY
   pt_cornell.npz     <- oracle/_ref/ref_render (reference PathIntegrator + kd-tree through the C API,
                         threads=1, tiles linear) on scenes_pt.cornell_box for the PT_GOLDEN configurations
@@ -46,6 +47,15 @@ PT_GOLDEN_DOF = {
 }
 
 
+# directional (infinite + finite beam), sunlight and spherelight next to the ceiling area light -> pt_lights.npz
+PT_GOLDEN_LIGHTS = {
+    "five_lights": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, light_samples=2,
+                        extra_lights=("sun", "directional", "directional_finite", "sphere")),
+    "sun_sphere_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", light_samples=3,
+                              point_light=True, extra_lights=("sun", "sphere"), filter_type="gauss"),
+}
+
+
 def make_extra(configs, filename):
     from libyafaray_b200 import scenes_pt
 
@@ -60,6 +70,7 @@ def make_extra(configs, filename):
 def make_city():
     make_extra(PT_GOLDEN_CITY, "pt_city.npz")
     make_extra(PT_GOLDEN_DOF, "pt_dof.npz")
+    make_extra(PT_GOLDEN_LIGHTS, "pt_lights.npz")
 
 
 def main():

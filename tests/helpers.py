@@ -104,10 +104,23 @@ def emu_film_flags(a, w, rgba, aa):
     return idx
 
 
-def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0, shard_index=0, shard_count=1, pixel_list=None, film=None):
+def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0, shard_index=0, shard_count=1, pixel_list=None, film=None, ref_light_order=False):
     """CPU emulation of the wavefront path tracer stages on an Interface.assemble() result -> (weights, rgba).
-    pixel_list: adaptive pass over these pixels only; film: (weights, rgba) to accumulate into."""
+    pixel_list: adaptive pass over these pixels only; film: (weights, rgba) to accumulate into.
+    ref_light_order: pick the one-light-per-vertex lights with the reference's single-thread call counter (threads=1,
+    linear tiles of 32) instead of the product's per-vertex index -- sample-exact comparisons of multi-light scenes."""
     import ctypes as C
+
+    if ref_light_order:
+        assert pixel_list is None and film is None and shard_count == 1
+        emu().emu_light_choice_mode(1)
+        emu_pt_render(a, n_samples, offset, aa_pass)
+        emu().emu_light_choice_finalize(C.c_int(a["params"].width), C.c_int(32))
+        emu().emu_light_choice_mode(2)
+        try:
+            return emu_pt_render(a, n_samples, offset, aa_pass)
+        finally:
+            emu().emu_light_choice_mode(0)
 
     pr = a["params"]
     n_samples = pr.aa_samples if n_samples is None else n_samples
