@@ -150,21 +150,22 @@ typedef struct y4gpu_pt_material
 } y4gpu_pt_material;
 
 /* pointlight (light_point.cc), arealight (light_area.cc), directional (light_directional.cc), sunlight (light_sun.cc),
-   spherelight (light_sphere.cc; light sampling only, like the reference: canIntersect() is false) */
-enum { Y4GPU_LIGHT_POINT = 0, Y4GPU_LIGHT_AREA = 1, Y4GPU_LIGHT_DIRECTIONAL = 2, Y4GPU_LIGHT_SUN = 3, Y4GPU_LIGHT_SPHERE = 4 };
+   spherelight (light_sphere.cc; light sampling only, like the reference: canIntersect() is false),
+   spotlight without soft_shadows (light_spot.cc: a dirac light with a smoothstep cone) */
+enum { Y4GPU_LIGHT_POINT = 0, Y4GPU_LIGHT_AREA = 1, Y4GPU_LIGHT_DIRECTIONAL = 2, Y4GPU_LIGHT_SUN = 3, Y4GPU_LIGHT_SPHERE = 4, Y4GPU_LIGHT_SPOT = 5 };
 typedef struct y4gpu_pt_light
 {
 	int32_t type;                 /* Y4GPU_LIGHT_* ; lights in the reference's (name-sorted) order */
-	float from[3];                /* pointlight / spherelight / finite directional `from`, arealight `corner` */
-	float point1[3], point2[3];   /* arealight `point1`, `point2`; directional / sunlight: point1 = `direction` (towards the light) */
+	float from[3];                /* pointlight / spherelight / spotlight / finite directional `from`, arealight `corner` */
+	float point1[3], point2[3];   /* arealight `point1`, `point2`; directional / sunlight: point1 = `direction` (towards the light); spotlight: point1 = `to` */
 	float color[3];
 	float power;
 	int32_t samples;              /* arealight / sunlight / spherelight `samples` */
 	int32_t cast_shadows;         /* default 1 */
 	float radius;                 /* spherelight `radius`; directional `radius` when !infinite */
-	float angle;                  /* sunlight `angle` in degrees (default 0.27) */
+	float angle;                  /* sunlight `angle` (default 0.27) / spotlight `cone_angle` (default 45), degrees */
 	int32_t infinite;             /* directional `infinite` (default 1) */
-	int32_t reserved[1];
+	float blend;                  /* spotlight `blend` (default 0.15) */
 } y4gpu_pt_light;
 
 typedef struct y4gpu_pt_camera    /* `perspective` camera parameters (camera_perspective.cc:182-220) */

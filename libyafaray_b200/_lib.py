@@ -46,7 +46,7 @@ class PtMaterial(C.Structure):
 class PtLight(C.Structure):
     _fields_ = [("type", C.c_int32), ("from_", C.c_float * 3), ("point1", C.c_float * 3), ("point2", C.c_float * 3),
                 ("color", C.c_float * 3), ("power", C.c_float), ("samples", C.c_int32), ("cast_shadows", C.c_int32),
-                ("radius", C.c_float), ("angle", C.c_float), ("infinite", C.c_int32), ("reserved", C.c_int32 * 1)]  # fmt: skip
+                ("radius", C.c_float), ("angle", C.c_float), ("infinite", C.c_int32), ("blend", C.c_float)]  # fmt: skip
 
 
 class PtCamera(C.Structure):
@@ -81,7 +81,7 @@ class PtAaNoise(C.Structure):
 
 
 MAT_SHINYDIFFUSE, MAT_LIGHT = 0, 1
-LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE = 0, 1, 2, 3, 4
+LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT = 0, 1, 2, 3, 4, 5
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
 
 

@@ -246,7 +246,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	for(uint32_t i = 0; i < n_mat; ++i)
 		if(mats[i].type != Y4GPU_MAT_SHINYDIFFUSE && mats[i].type != Y4GPU_MAT_LIGHT) { ctx->err = "unsupported material type"; return Y4GPU_ERR_UNSUPPORTED; }
 	for(uint32_t i = 0; i < n_light; ++i)
-		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_SPHERE) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
+		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_SPOT) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	if(!ctx->pt) ctx->pt = new Y4Pt;
 	if(const char *e = getenv("Y4GPU_PT_MIN_BLOCKS")) ctx->pt->stage_min_blocks = atoi(e);

@@ -111,6 +111,16 @@ inline Y4PtLight derive_light(const y4gpu_pt_light &l)
 		o.color = c3(o.color.r * o.pdf, o.color.g * o.pdf, o.color.b * o.pdf);            // col_pdf_
 		return o;
 	}
+	if(l.type == Y4GPU_LIGHT_SPOT)                        // SpotLight ctor (light_spot.cc:30-43), soft_shadows_ == false
+	{
+		o.dir = tov(normalized(hv(l.from) - hv(l.point1)));                                // ndir_ = (from - to).normalize()
+		const double rad_angle = (double) (float) ((long double) l.angle * 0.01745329251994329576923690768489L);
+		const double rad_inner_angle = rad_angle * (double) (1.f - l.blend);
+		o.cos_start = y4_fast_cos((float) rad_inner_angle);
+		o.cos_end = y4_fast_cos((float) rad_angle);
+		o.icos_diff = 1.f / (o.cos_start - o.cos_end);
+		return o;
+	}
 	if(l.type == Y4GPU_LIGHT_SPHERE)                      // SphereLight ctor (light_sphere.cc:30-40)
 	{
 		o.radius = l.radius;

@@ -1,6 +1,6 @@
 // Per-vertex shading logic of the wavefront path tracer: surface set-up, the supported
 // materials (shinydiffusemat without mirror/transparency/translucency/nodes, light_mat), the
-// supported lights (pointlight, arealight, directional, sunlight, spherelight) and one direct-light sample with MIS.  Restated from
+// supported lights (pointlight, arealight, directional, sunlight, spherelight, spotlight) and one direct-light sample with MIS.  Restated from
 // the reference operation for operation (never-contracted fp32, see y4_common.cuh):
 //   TrianglePrimitive::getSurface              src/geometry/primitive/primitive_triangle.cc:97-176
 //   ShinyDiffuseMaterial::sample/eval/pdf/emit src/material/material_shiny_diffuse.cc:197-385
@@ -185,11 +185,12 @@ Y4_HD bool y4_sphere_intersect(const V3 from, const V3 dir, const V3 c, float r2
 	return true;
 }
 
-// Light::illuminate of the dirac lights: PointLight (light_point.cc:38-57), DirectionalLight (light_directional.cc:58-80)
+// Light::illuminate of the dirac lights: PointLight (light_point.cc:38-57), SpotLight without soft shadows
+// (light_spot.cc:74-104), DirectionalLight (light_directional.cc:58-80)
 Y4_HD bool y4_light_illuminate(const Y4PtLight &L, const V3 p, Y4LSample &ls)
 {
 	ls.pdf = 1.f;
-	if(L.type == Y4GPU_LIGHT_POINT)
+	if(L.type == Y4GPU_LIGHT_POINT || L.type == Y4GPU_LIGHT_SPOT)
 	{
 		V3 ldir = xsub3(L.pos, p);
 		const float dist_sqr = xadd(xadd(xmul(ldir.x, ldir.x), xmul(ldir.y, ldir.y)), xmul(ldir.z, ldir.z));
@@ -198,7 +199,14 @@ Y4_HD bool y4_light_illuminate(const Y4PtLight &L, const V3 p, Y4LSample &ls)
 		const float idist_sqr = xdiv(1.f, dist_sqr);
 		ls.dir = xscale(ldir, xdiv(1.f, dist));
 		ls.tmax = dist;
-		ls.col = cscale(L.color, idist_sqr);
+		if(L.type == Y4GPU_LIGHT_POINT) { ls.col = cscale(L.color, idist_sqr); return true; }
+		// SpotLight::illuminate (light_spot.cc:74-104): smoothstep between cos_end_ and cos_start_
+		const float cosa = xdot(L.dir, ls.dir);
+		if(cosa < L.cos_end) return false;
+		if(cosa >= L.cos_start) { ls.col = cscale(L.color, idist_sqr); return true; }
+		float v = xmul(xsub(cosa, L.cos_end), L.icos_diff);
+		v = xmul(xmul(v, v), xsub(3.f, xmul(2.f, v)));
+		ls.col = cscale(cscale(L.color, v), idist_sqr);                 // color_ * v * idist_sqr
 		return true;
 	}
 	// directional

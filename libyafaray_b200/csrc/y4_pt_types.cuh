@@ -60,11 +60,12 @@ struct Y4PtLight
 	// directional (light_directional.cc:28-39), sun (light_sun.cc:29-43), sphere (light_sphere.cc:30-40)
 	V3 dir, du, dv;             // normalised direction towards the light; sun: frame of the *unnormalised* ctor argument
 	float cos_angle, pdf, invpdf;
+	float cos_start, cos_end, icos_diff;   // spot (light_spot.cc:30-43); its ndir_ is kept in `dir`
 	float radius, sq_radius, sq_radius_eps;
 	int infinite;
 };
 // Light::diracLight() / Light::canIntersect() of the supported lights (include/light/light_*.h)
-Y4_HD bool y4_light_dirac(int type) { return type == Y4GPU_LIGHT_POINT || type == Y4GPU_LIGHT_DIRECTIONAL; }
+Y4_HD bool y4_light_dirac(int type) { return type == Y4GPU_LIGHT_POINT || type == Y4GPU_LIGHT_DIRECTIONAL || type == Y4GPU_LIGHT_SPOT; }
 Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN; }
 
 #define Y4_PT_MAX_LIGHTS 64

@@ -109,8 +109,10 @@ class Interface:
 
     def createLight(self, name):
         p = dict(self.params)
-        if p.get("type") not in ("pointlight", "arealight", "directional", "sunlight", "spherelight"):
+        if p.get("type") not in ("pointlight", "arealight", "directional", "sunlight", "spherelight", "spotlight"):
             raise Y4Error(f"light type '{p.get('type')}' is not supported by the GPU back end")
+        if p.get("type") == "spotlight" and p.get("soft_shadows", False):
+            raise Y4Error("spotlight soft_shadows is not supported by the GPU back end")
         self.lights[name] = p
         return True
 
@@ -335,6 +337,10 @@ class Interface:
             elif p["type"] == "sunlight":          # SunLight::factory (light_sun.cc:97-128)
                 l.type, l.samples, l.angle = _lib.LIGHT_SUN, int(p.get("samples", 4)), float(p.get("angle", 0.27))
                 l.point1[:] = p.get("direction", (0.0, 0.0, 1.0))
+            elif p["type"] == "spotlight":         # SpotLight::factory (light_spot.cc:250-288), soft_shadows = false
+                l.type, l.angle, l.blend = _lib.LIGHT_SPOT, float(p.get("cone_angle", 45.0)), float(p.get("blend", 0.15))
+                l.from_[:] = p.get("from", (0.0, 0.0, 0.0))
+                l.point1[:] = p.get("to", (0.0, 0.0, -1.0))
             elif p["type"] == "spherelight":       # SphereLight::factory (light_sphere.cc:160-195)
                 l.type, l.samples, l.radius = _lib.LIGHT_SPHERE, int(p.get("samples", 4)), float(p.get("radius", 1.0))
                 l.from_[:] = p.get("from", (0.0, 0.0, 0.0))

@@ -62,7 +62,7 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
                 oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=()):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
-    extra_lights: any of "sun", "directional", "directional_finite", "sphere" shining in through the open front."""
+    extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
     _material(api, "white", white, **extra)
@@ -134,6 +134,14 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
             api.paramsSetFloat("radius", 0.22)
             api.paramsSetColor("color", 1.0, 0.4, 0.3, 1.0)
             api.paramsSetFloat("power", 1.5)
+        elif kind == "spot":                            # from the front opening onto the short box, wide blend
+            api.paramsSetString("type", "spotlight")
+            api.paramsSetVector("from", 0.75, 0.6, -0.9)
+            api.paramsSetVector("to", 0.35, 0.2, 0.4)
+            api.paramsSetFloat("cone_angle", 14.0)
+            api.paramsSetFloat("blend", 0.5)
+            api.paramsSetColor("color", 0.9, 0.6, 1.0, 1.0)
+            api.paramsSetFloat("power", 2.5)
         elif kind == "sphere":
             api.paramsSetString("type", "spherelight")
             api.paramsSetVector("from", 0.2, 0.75, 0.3)

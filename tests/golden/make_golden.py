@@ -49,10 +49,10 @@ PT_GOLDEN_DOF = {
 
 # directional (infinite + finite beam), sunlight and spherelight next to the ceiling area light -> pt_lights.npz
 PT_GOLDEN_LIGHTS = {
-    "five_lights": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, light_samples=2,
-                        extra_lights=("sun", "directional", "directional_finite", "sphere")),
-    "sun_sphere_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", light_samples=3,
-                              point_light=True, extra_lights=("sun", "sphere"), filter_type="gauss"),
+    "six_lights": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, light_samples=2,
+                        extra_lights=("sun", "directional", "directional_finite", "sphere", "spot")),
+    "sun_sphere_spot_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", light_samples=3,
+                              point_light=True, extra_lights=("sun", "sphere", "spot"), filter_type="gauss"),
 }
 
 

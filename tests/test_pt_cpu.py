@@ -33,7 +33,7 @@ def test_stages_vs_golden_reference_render(key):
     """Cornell configurations and the instanced mini-city (C4: yafaray_addInstance, sky background)."""
     ref = np.load(os.path.join(GOLD, ALL_GOLDEN[key][0]))[key]
     # with several lights the path vertices pick one light each from the reference's single-thread call counter:
-    # replayed here (helpers.emu_pt_render) so that the five-light scene is compared sample for sample
+    # replayed here (helpers.emu_pt_render) so that the six-light scene is compared sample for sample
     a = _assemble(**ALL_GOLDEN[key][1])
     w, rgba = helpers.emu_pt_render(a, ref_light_order=a["n_light"] > 1 and a["params"].path_samples > 0)
     img = interface.normalize_film(w, rgba)
@@ -125,7 +125,12 @@ def test_interface_rejects_unsupported_features():
     with pytest.raises(Y4Error):
         yi.createCamera("c")
     yi.paramsClearAll()
+    yi.paramsSetString("type", "meshlight")
+    with pytest.raises(Y4Error):
+        yi.createLight("l")
+    yi.paramsClearAll()
     yi.paramsSetString("type", "spotlight")
+    yi.paramsSetBool("soft_shadows", True)
     with pytest.raises(Y4Error):
         yi.createLight("l")
     yi.paramsClearAll()
@@ -232,24 +237,22 @@ def test_fast_sampling_forms_equal_the_pinned_recurrences():
 def test_light_choice_index_is_an_equally_good_estimator():
     """The product numbers estimateOneDirectLight's draws per vertex (the reference's per-thread counter depends on
     thread scheduling).  Same estimator, different low-discrepancy index: the converged images agree."""
-    kw = dict(PT_GOLDEN_LIGHTS["five_lights"], spp=48)
+    kw = dict(PT_GOLDEN_LIGHTS["six_lights"], spp=48)
     a = _assemble(**kw)
     own = interface.normalize_film(*helpers.emu_pt_render(a))
     ref = interface.normalize_film(*helpers.emu_pt_render(a, ref_light_order=True))
     assert not np.array_equal(own, ref)
     lit = ref[..., :3].sum(-1) > 0.05
     assert abs(float(own[..., :3][lit].mean() / ref[..., :3][lit].mean()) - 1.0) < 0.01
-    assert helpers.psnr(np.clip(own, 0, 2), np.clip(ref, 0, 2), peak=2.0) > 30.0
+    assert helpers.psnr(np.clip(own, 0, 2), np.clip(ref, 0, 2), peak=2.0) > 27.0   # noise-limited at 48 spp with six lights
 
 
-def test_new_light_types_derive_like_the_reference_constructors():
+def test_light_types_are_exported_in_name_order_with_their_parameters():
     yi = interface.Interface()
-    scenes_pt.build(yi, accelerator="yafaray-b200-bvh8", **PT_GOLDEN_LIGHTS["five_lights"])
+    scenes_pt.build(yi, accelerator="yafaray-b200-bvh8", **PT_GOLDEN_LIGHTS["six_lights"])
     a = yi.assemble()
     from libyafaray_b200 import _lib
-    kinds = [a["lights"][i].type for i in range(a["n_light"])]      # name order: lamp, x_directional, x_directional_finite, x_sphere, x_sun
-    assert kinds == [_lib.LIGHT_AREA, _lib.LIGHT_DIRECTIONAL, _lib.LIGHT_DIRECTIONAL, _lib.LIGHT_SPHERE, _lib.LIGHT_SUN]
+    kinds = [a["lights"][i].type for i in range(a["n_light"])]      # name order: lamp, x_directional, x_directional_finite, x_sphere, x_spot, x_sun
+    assert kinds == [_lib.LIGHT_AREA, _lib.LIGHT_DIRECTIONAL, _lib.LIGHT_DIRECTIONAL, _lib.LIGHT_SPHERE, _lib.LIGHT_SPOT, _lib.LIGHT_SUN]
     assert a["lights"][1].infinite == 1 and a["lights"][2].infinite == 0 and abs(a["lights"][2].radius - 0.22) < 1e-7
-    assert abs(a["lights"][4].angle - 4.0) < 1e-7 and a["lights"][3].samples == 2
-    with pytest.raises(Y4Error):
-        yi.paramsClearAll(); yi.paramsSetString("type", "spotlight"); yi.createLight("s")
+    assert abs(a["lights"][5].angle - 4.0) < 1e-7 and a["lights"][3].samples == 2 and abs(a["lights"][4].blend - 0.5) < 1e-7

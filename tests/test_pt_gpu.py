@@ -53,13 +53,13 @@ def test_gpu_five_light_types_vs_cpu_emulation_and_reference_statistics():
     """directional (infinite + beam), sunlight, spherelight, arealight under path tracing: the device film equals the
     emulation's (which tests/test_pt_cpu.py pins sample-exactly to the reference render), and at higher spp the image
     converges to the reference golden's brightness."""
-    kw = PT_GOLDEN_LIGHTS["five_lights"]
+    kw = PT_GOLDEN_LIGHTS["six_lights"]
     yi = _gpu(**kw)
     img = yi.render()
     w, rgba = yi.read_film()
     we, re = helpers.emu_pt_render(yi._assembled)
     assert np.allclose(w, we, rtol=0, atol=1e-5) and np.allclose(rgba, re, rtol=1e-5, atol=2e-5)
-    ref = np.load(os.path.join(GOLD, "pt_lights.npz"))["five_lights"]
+    ref = np.load(os.path.join(GOLD, "pt_lights.npz"))["six_lights"]
     assert img.shape == ref.shape
     hi = _gpu(**dict(kw, spp=64)).render()
     lit = ref[..., :3].sum(-1) > 0.05
