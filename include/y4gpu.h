@@ -146,8 +146,57 @@ typedef struct y4gpu_pt_material
 	int32_t double_sided;         /* light_mat */
 	int32_t receive_shadows;      /* default 1 */
 	int32_t flat_material;        /* default 0 */
-	int32_t reserved[5];
+	int32_t layer_first, layer_count;   /* shinydiffusemat `diffuse_shader`: its chain of layer nodes in y4gpu_pt_set_textures'
+	                                       layer array, bottom layer first (layer_count == 0: plain `color`) */
+	int32_t reserved[3];
 } y4gpu_pt_material;
+
+/* Image textures and the `diffuse_shader` node chains of shinydiffusemat: texture_mapper + layer nodes
+ * (src/shader/shader_node_basic.cc:31-367, shader_node_layer.cc:30-351) over ImageTexture (src/texture/texture_image.cc).
+ * Supported: texco uv / orco / global, mapping plain / cube, interpolate none / bilinear, every clipping mode, the
+ * intensity / contrast / per-channel / clamp adjustments, every layer blend mode, colour inputs.  Anything else
+ * (procedural textures, bicubic / mipmap interpolation, tube / sphere mapping, hue / saturation, scalar inputs, bump
+ * and the other shader slots) is rejected by the host mirror, never approximated. */
+enum { Y4GPU_CLIP_EXTEND = 0, Y4GPU_CLIP_CLIP = 1, Y4GPU_CLIP_CLIPCUBE = 2, Y4GPU_CLIP_REPEAT = 3, Y4GPU_CLIP_CHECKER = 4 };
+enum { Y4GPU_INTERP_NONE = 0, Y4GPU_INTERP_BILINEAR = 1 };
+typedef struct y4gpu_pt_texture
+{
+	const float *texels;          /* width * height RGBA floats, row-major (x fastest), exactly what Image::getColor(x, y) returns:
+	                                 linear RGB after the colour-space conversion and the storage rounding of the image's
+	                                 optimization mode (include/image/image_buffers.h); host or device memory, copied by the call */
+	int32_t width, height;
+	int32_t clip;                 /* Y4GPU_CLIP_* (`clipping`, default repeat) */
+	int32_t interpolate;          /* Y4GPU_INTERP_* (`interpolate`, default bilinear) */
+	int32_t xrepeat, yrepeat, mirror_x, mirror_y, rot90;
+	float cropmin_x, cropmin_y, cropmax_x, cropmax_y;
+	int32_t even_tiles, odd_tiles; float checker_dist;
+	float adj_intensity, adj_contrast, adj_mult_factor_red, adj_mult_factor_green, adj_mult_factor_blue;
+	int32_t adj_clamp;
+	int32_t reserved[4];
+} y4gpu_pt_texture;
+
+enum { Y4GPU_TEXCO_GLOBAL = 0, Y4GPU_TEXCO_UV = 1, Y4GPU_TEXCO_ORCO = 2 };
+enum { Y4GPU_PROJ_PLAIN = 0, Y4GPU_PROJ_CUBE = 1 };
+enum { Y4GPU_BLEND_MIX = 0, Y4GPU_BLEND_ADD = 1, Y4GPU_BLEND_MULT = 2, Y4GPU_BLEND_SUB = 3, Y4GPU_BLEND_SCREEN = 4,
+       Y4GPU_BLEND_DIV = 5, Y4GPU_BLEND_DIFF = 6, Y4GPU_BLEND_DARK = 7, Y4GPU_BLEND_LIGHT = 8 };
+enum { Y4GPU_LAYER_RGB_TO_INT = 1, Y4GPU_LAYER_STENCIL = 2, Y4GPU_LAYER_NEGATIVE = 4 };
+typedef struct y4gpu_pt_layer     /* one `layer` node together with the `texture_mapper` node on its input */
+{
+	/* texture_mapper (TextureMapperNode::factory, shader_node_basic.cc:306-367) */
+	int32_t texture;              /* index into the texture array */
+	int32_t texco;                /* Y4GPU_TEXCO_* */
+	int32_t mapping;              /* Y4GPU_PROJ_* */
+	int32_t proj_x, proj_y, proj_z;   /* 0..3 (default 1, 2, 3) */
+	float scale[3], offset[3];    /* `offset` as given (the library doubles it like the reference) */
+	/* layer (LayerNode::factory, shader_node_layer.cc:301-349) */
+	int32_t flags;                /* Y4GPU_LAYER_*: noRGB, stencil, negative */
+	int32_t blend_mode;           /* Y4GPU_BLEND_* */
+	int32_t do_color;             /* default 1 */
+	float colfac;                 /* default 1 */
+	float def_col[3];             /* default 1, 1, 1 */
+	float upper_color[4];         /* bottom layer only: `upper_color` (default 0, 0, 0, 0) */
+	int32_t reserved[4];
+} y4gpu_pt_layer;
 
 /* pointlight (light_point.cc), arealight (light_area.cc), directional (light_directional.cc), sunlight (light_sun.cc),
    spherelight (light_sphere.cc; light sampling only, like the reference: canIntersect() is false),
@@ -236,6 +285,13 @@ typedef struct y4gpu_pt_aa_noise
 /* Per-triangle material index travels in the flag word of y4gpu_upload_triangles (bits 8..31).
  * vertex_normals: n_tri*9 floats (exported normals: shading normal interpolated like
  * primitive_triangle.cc:104-114) or NULL for flat shading. */
+/* Textures, layer chains and the per-triangle texture coordinates they read; call after y4gpu_build and BEFORE
+ * y4gpu_pt_set_scene (materials refer to layers by index).  tri_orco: n_tri*9 floats, the three orco points of every
+ * triangle (yafaray_addVertexWithOrco), a NaN in the first float marks a triangle of a mesh without orco points
+ * (orco = hit point, primitive_triangle.cc:122-127); tri_uv: n_tri*6 floats (yafaray_addUv / addTriangleWithUv), NaN
+ * = no uv (implicit barycentric mapping).  Either may be NULL.  n_tex == 0 and n_layers == 0 removes everything. */
+int y4gpu_pt_set_textures(y4gpu_ctx *ctx, const y4gpu_pt_texture *textures, uint32_t n_tex, const y4gpu_pt_layer *layers,
+                          uint32_t n_layers, const float *tri_orco, const float *tri_uv);
 int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_pt_material *mats, uint32_t n_mat,
                        const y4gpu_pt_light *lights, uint32_t n_light, const y4gpu_pt_params *params,
                        const float *vertex_normals);

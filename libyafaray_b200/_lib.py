@@ -40,7 +40,24 @@ class Stats(C.Structure):
 class PtMaterial(C.Structure):
     _fields_ = [("type", C.c_int32), ("color", C.c_float * 3), ("diffuse_reflect", C.c_float), ("emit", C.c_float),
                 ("oren_nayar", C.c_int32), ("sigma", C.c_float), ("double_sided", C.c_int32), ("receive_shadows", C.c_int32),
-                ("flat_material", C.c_int32), ("reserved", C.c_int32 * 5)]  # fmt: skip
+                ("flat_material", C.c_int32), ("layer_first", C.c_int32), ("layer_count", C.c_int32), ("reserved", C.c_int32 * 3)]  # fmt: skip
+
+
+class PtTexture(C.Structure):
+    _fields_ = [("texels", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32), ("clip", C.c_int32), ("interpolate", C.c_int32),
+                ("xrepeat", C.c_int32), ("yrepeat", C.c_int32), ("mirror_x", C.c_int32), ("mirror_y", C.c_int32), ("rot90", C.c_int32),
+                ("cropmin_x", C.c_float), ("cropmin_y", C.c_float), ("cropmax_x", C.c_float), ("cropmax_y", C.c_float),
+                ("even_tiles", C.c_int32), ("odd_tiles", C.c_int32), ("checker_dist", C.c_float),
+                ("adj_intensity", C.c_float), ("adj_contrast", C.c_float), ("adj_mult_factor_red", C.c_float),
+                ("adj_mult_factor_green", C.c_float), ("adj_mult_factor_blue", C.c_float), ("adj_clamp", C.c_int32),
+                ("reserved", C.c_int32 * 4)]  # fmt: skip
+
+
+class PtLayer(C.Structure):
+    _fields_ = [("texture", C.c_int32), ("texco", C.c_int32), ("mapping", C.c_int32), ("proj_x", C.c_int32), ("proj_y", C.c_int32),
+                ("proj_z", C.c_int32), ("scale", C.c_float * 3), ("offset", C.c_float * 3), ("flags", C.c_int32), ("blend_mode", C.c_int32),
+                ("do_color", C.c_int32), ("colfac", C.c_float), ("def_col", C.c_float * 3), ("upper_color", C.c_float * 4),
+                ("reserved", C.c_int32 * 4)]  # fmt: skip
 
 
 class PtLight(C.Structure):
@@ -83,6 +100,12 @@ class PtAaNoise(C.Structure):
 MAT_SHINYDIFFUSE, MAT_LIGHT = 0, 1
 LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT = 0, 1, 2, 3, 4, 5
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
+CLIP_MODES = {"extend": 0, "clip": 1, "clipcube": 2, "repeat": 3, "checker": 4}
+INTERPOLATIONS = {"none": 0, "bilinear": 1}
+TEXCO = {"global": 0, "uv": 1, "orco": 2}
+PROJECTIONS = {"plain": 0, "cube": 1}
+BLEND_MODES = {"mix": 0, "add": 1, "multiply": 2, "subtract": 3, "screen": 4, "divide": 5, "difference": 6, "darken": 7, "lighten": 8}
+LAYER_RGB_TO_INT, LAYER_STENCIL, LAYER_NEGATIVE = 1, 2, 4
 
 
 class Y4Error(RuntimeError):
@@ -98,7 +121,7 @@ EXPORTED = [
     "y4gpu_upload_triangles", "y4gpu_build", "y4gpu_get_bound",
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow",
     "y4gpu_get_stats", "y4gpu_synchronize",
-    "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
+    "y4gpu_pt_set_textures", "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
     "y4gpu_pt_read_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass",
 ]  # fmt: skip
 
@@ -144,6 +167,8 @@ def lib() -> C.CDLL:
     L.y4gpu_synchronize.restype = i32
     L.y4gpu_pt_set_scene.argtypes = [vp, C.POINTER(PtCamera), C.POINTER(PtMaterial), u32, C.POINTER(PtLight), u32, C.POINTER(PtParams), vp]
     L.y4gpu_pt_set_scene.restype = i32
+    L.y4gpu_pt_set_textures.argtypes = [vp, C.POINTER(PtTexture), u32, C.POINTER(PtLayer), u32, vp, vp]
+    L.y4gpu_pt_set_textures.restype = i32
     L.y4gpu_pt_set_film_buffers.argtypes = [vp, vp, vp]
     L.y4gpu_pt_set_film_buffers.restype = i32
     L.y4gpu_pt_clear_film.argtypes = [vp]

@@ -19,6 +19,10 @@ struct Y4Pt
 	float4 *d_tri_shade = nullptr;
 	uint32_t mats_cap = 0, lights_cap = 0; uint64_t tri_cap = 0, normals_cap = 0; size_t film_cap = 0;
 	float *d_normals = nullptr;
+	// textures (y4gpu_pt_set_textures): one texel allocation per texture, the derived texture / layer tables, per-triangle orco / uv
+	std::vector<float4 *> d_texels;
+	Y4PtTexture *d_textures = nullptr; Y4PtLayer *d_layers = nullptr; float *d_tri_orco = nullptr, *d_tri_uv = nullptr;
+	uint32_t n_textures = 0, n_layers = 0;
 	uint8_t *d_sigma = nullptr; uint16_t *d_offset = nullptr, *d_prime = nullptr; double *d_inv_prime = nullptr, *d_sigma_d = nullptr; unsigned long long *d_magic = nullptr;
 	bool scene_set = false;
 	y4gpu_pt_params params = {};
@@ -55,6 +59,15 @@ struct Y4Pt
 };
 
 #include "y4_pt_host.h"
+
+static void pt_free_textures(Y4Pt *pt)
+{
+	for(float4 *p : pt->d_texels) cudaFree(p);
+	pt->d_texels.clear();
+	cudaFree(pt->d_textures); cudaFree(pt->d_layers); cudaFree(pt->d_tri_orco); cudaFree(pt->d_tri_uv);
+	pt->d_textures = nullptr; pt->d_layers = nullptr; pt->d_tri_orco = nullptr; pt->d_tri_uv = nullptr;
+	pt->n_textures = pt->n_layers = 0;
+}
 
 // ---- kernels -------------------------------------------------------------------------------------------
 // Dense kernels (camera rays, splat) run one thread per pixel-sample of the wave.  Stage kernels run one
@@ -221,6 +234,7 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	for(int l = 1; l < kMaxLanes; ++l) if(pt->lanes[l].stream) cudaStreamDestroy(pt->lanes[l].stream);
 	if(pt->ev_fork) cudaEventDestroy(pt->ev_fork);
 	cudaFree(pt->d_lights); cudaFree(pt->d_mats); cudaFree(pt->d_normals); cudaFree(pt->d_tri_shade);
+	pt_free_textures(pt);
 	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime); cudaFree(pt->d_sigma_d); cudaFree(pt->d_magic);
 	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); cudaFree(pt->d_pixel_list);
 	cudaFree(pt->d_counters); cudaFreeHost(pt->h_counters);
@@ -230,6 +244,71 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	for(cudaEvent_t e : pt->prof_events) cudaEventDestroy(e);
 	delete pt;
 	ctx->pt = nullptr;
+}
+
+int y4gpu_pt_set_textures(y4gpu_ctx *ctx, const y4gpu_pt_texture *textures, uint32_t n_tex, const y4gpu_pt_layer *layers, uint32_t n_layers,
+                          const float *tri_orco, const float *tri_uv)
+{
+	if(!ctx || (n_tex && !textures) || (n_layers && !layers)) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	if(!ctx->built) { ctx->err = "y4gpu_pt_set_textures before y4gpu_build"; return Y4GPU_ERR_ARG; }
+	for(uint32_t i = 0; i < n_tex; ++i)
+	{
+		const y4gpu_pt_texture &t = textures[i];
+		if(!t.texels || t.width < 1 || t.height < 1) { ctx->err = "texture without texels"; return Y4GPU_ERR_ARG; }
+		if(t.clip < Y4GPU_CLIP_EXTEND || t.clip > Y4GPU_CLIP_CHECKER || (t.interpolate != Y4GPU_INTERP_NONE && t.interpolate != Y4GPU_INTERP_BILINEAR))
+		{ ctx->err = "unsupported texture clipping / interpolation"; return Y4GPU_ERR_UNSUPPORTED; }
+	}
+	for(uint32_t i = 0; i < n_layers; ++i)
+	{
+		const y4gpu_pt_layer &l = layers[i];
+		if(l.texture < 0 || (uint32_t) l.texture >= n_tex) { ctx->err = "layer refers to a texture that does not exist"; return Y4GPU_ERR_ARG; }
+		if(l.texco < Y4GPU_TEXCO_GLOBAL || l.texco > Y4GPU_TEXCO_ORCO || l.mapping < Y4GPU_PROJ_PLAIN || l.mapping > Y4GPU_PROJ_CUBE || l.blend_mode < Y4GPU_BLEND_MIX || l.blend_mode > Y4GPU_BLEND_LIGHT)
+		{ ctx->err = "unsupported texture_mapper / layer mode"; return Y4GPU_ERR_UNSUPPORTED; }
+	}
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	if(!ctx->pt) ctx->pt = new Y4Pt;
+	Y4Pt *pt = ctx->pt;
+	cudaStream_t st = ctx->stream;
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	pt_free_textures(pt);
+	pt->scene_set = false;                              // materials must be set again: they index the layer table
+	std::vector<Y4PtTexture> ht(n_tex);
+	for(uint32_t i = 0; i < n_tex; ++i)
+	{
+		ht[i] = derive_texture(textures[i]);
+		const size_t bytes = (size_t) textures[i].width * textures[i].height * sizeof(float4);
+		float4 *d = nullptr;
+		Y4_CUDA(ctx, cudaMalloc(&d, bytes));
+		pt->d_texels.push_back(d);
+		Y4_CUDA(ctx, cudaMemcpyAsync(d, textures[i].texels, bytes, cudaMemcpyDefault, st));
+		ht[i].texels = d;
+	}
+	std::vector<Y4PtLayer> hl(n_layers);
+	for(uint32_t i = 0; i < n_layers; ++i) hl[i] = derive_layer(layers[i]);
+	if(n_tex)
+	{
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_textures, n_tex * sizeof(Y4PtTexture)));
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_textures, ht.data(), n_tex * sizeof(Y4PtTexture), cudaMemcpyHostToDevice, st));
+	}
+	if(n_layers)
+	{
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_layers, n_layers * sizeof(Y4PtLayer)));
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_layers, hl.data(), n_layers * sizeof(Y4PtLayer), cudaMemcpyHostToDevice, st));
+	}
+	if(tri_orco && ctx->n_tri && n_layers)
+	{
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_tri_orco, ctx->n_tri * 9 * sizeof(float)));
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_tri_orco, tri_orco, ctx->n_tri * 9 * sizeof(float), cudaMemcpyDefault, st));
+	}
+	if(tri_uv && ctx->n_tri && n_layers)
+	{
+		Y4_CUDA(ctx, cudaMalloc(&pt->d_tri_uv, ctx->n_tri * 6 * sizeof(float)));
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_tri_uv, tri_uv, ctx->n_tri * 6 * sizeof(float), cudaMemcpyDefault, st));
+	}
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));            // the host vectors above go out of scope
+	pt->n_textures = n_tex; pt->n_layers = n_layers;
+	return Y4GPU_OK;
 }
 
 int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_pt_material *mats, uint32_t n_mat,
@@ -245,6 +324,9 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	if(params->path_samples < 0 || params->width < 1 || params->height < 1) { ctx->err = "bad path_samples / film size"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_mat; ++i)
 		if(mats[i].type != Y4GPU_MAT_SHINYDIFFUSE && mats[i].type != Y4GPU_MAT_LIGHT) { ctx->err = "unsupported material type"; return Y4GPU_ERR_UNSUPPORTED; }
+	for(uint32_t i = 0; i < n_mat; ++i)
+		if(mats[i].layer_count < 0 || (mats[i].layer_count > 0 && (mats[i].layer_first < 0 || !ctx->pt || (uint32_t) (mats[i].layer_first + mats[i].layer_count) > ctx->pt->n_layers)))
+		{ ctx->err = "material refers to layers that were not set (call y4gpu_pt_set_textures first)"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_light; ++i)
 		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_SPOT) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -317,6 +399,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		Y4_CUDA(ctx, cudaGetLastError());
 	}
 	sc.lights = pt->d_lights; sc.mats = pt->d_mats; sc.tri_shade = pt->d_tri_shade; sc.normals = pt->d_normals;
+	sc.textures = pt->d_textures; sc.layers = pt->d_layers; sc.tri_orco = pt->d_tri_orco; sc.tri_uv = pt->d_tri_uv;
 	sc.lds.sigma = pt->d_sigma; sc.lds.offset = pt->d_offset; sc.lds.prime = pt->d_prime; sc.lds.inv_prime = pt->d_inv_prime; sc.lds.sigma_d = pt->d_sigma_d; sc.lds.magic = pt->d_magic;
 	// film (internal unless the caller installs buffers)
 	const size_t npx = (size_t) sc.width * sc.height;

@@ -65,6 +65,7 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 		return o;
 	}
 	o.color = c3(m.color[0], m.color[1], m.color[2]);
+	o.layer_first = m.layer_first; o.layer_count = m.layer_count; o.emit_strength = m.emit;
 	o.emit = c3(m.emit * m.color[0], m.emit * m.color[1], m.emit * m.color[2]);
 	if(m.emit > 0.f) o.bsdf_flags |= Y4_BSDF_EMIT;
 	const float acc = 1.f;                                    // no mirror / transparency / translucency components
@@ -80,6 +81,40 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 		o.oren_b = (float) (0.45 * s2 / (s2 + 0.09));
 		o.oren_nayar = 1;
 	}
+	return o;
+}
+
+// ImageTexture::factory state (texture_image.cc:476-597: setCrop, setAdjustments); texels are set by the caller
+inline Y4PtTexture derive_texture(const y4gpu_pt_texture &t)
+{
+	Y4PtTexture o;
+	memset(&o, 0, sizeof(o));
+	o.w = t.width; o.h = t.height; o.clip = t.clip; o.interp = t.interpolate;
+	o.xrepeat = t.xrepeat; o.yrepeat = t.yrepeat; o.mirror_x = t.mirror_x; o.mirror_y = t.mirror_y; o.rot90 = t.rot90;
+	o.cropminx = t.cropmin_x; o.cropmaxx = t.cropmax_x; o.cropminy = t.cropmin_y; o.cropmaxy = t.cropmax_y;
+	o.cropx = (o.cropminx != 0.0) || (o.cropmaxx != 1.0);
+	o.cropy = (o.cropminy != 0.0) || (o.cropmaxy != 1.0);
+	o.checker_even = t.even_tiles; o.checker_odd = t.odd_tiles; o.checker_dist = t.checker_dist;
+	o.adj_intensity = t.adj_intensity; o.adj_contrast = t.adj_contrast; o.adj_clamp = t.adj_clamp;
+	o.adj_red = t.adj_mult_factor_red; o.adj_green = t.adj_mult_factor_green; o.adj_blue = t.adj_mult_factor_blue;
+	o.adjustments_set = t.adj_intensity != 1.f || t.adj_contrast != 1.f || t.adj_clamp || t.adj_mult_factor_red != 1.f || t.adj_mult_factor_green != 1.f || t.adj_mult_factor_blue != 1.f;
+	return o;
+}
+// TextureMapperNode::factory (shader_node_basic.cc:306-367) + LayerNode::factory / configInputs (shader_node_layer.cc:156-349)
+inline Y4PtLayer derive_layer(const y4gpu_pt_layer &l)
+{
+	Y4PtLayer o;
+	memset(&o, 0, sizeof(o));
+	o.tex = l.texture; o.coords = l.texco; o.projection = l.mapping;
+	const int map[3] = {l.proj_x, l.proj_y, l.proj_z};
+	int *dst[3] = {&o.map_x, &o.map_y, &o.map_z};
+	for(int k = 0; k < 3; ++k) *dst[k] = map[k] < 0 ? 0 : (map[k] > 3 ? 3 : map[k]);
+	o.scale = v3(l.scale[0], l.scale[1], l.scale[2]);
+	o.offset = v3(2 * l.offset[0], 2 * l.offset[1], 2 * l.offset[2]);
+	o.flags = (uint32_t) l.flags; o.blend = l.blend_mode; o.do_color = l.do_color; o.colfac = l.colfac;
+	for(int k = 0; k < 3; ++k) o.def_col[k] = l.def_col[k];
+	o.def_col[3] = 1.f;                                            // Rgba{def_col}
+	for(int k = 0; k < 4; ++k) o.upper_col[k] = l.upper_color[k];
 	return o;
 }
 

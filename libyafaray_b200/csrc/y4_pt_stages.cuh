@@ -8,6 +8,7 @@
 //   ImageFilm::addSample               src/render/imagefilm.cc:680-733
 #pragma once
 #include "y4_pt_shade.cuh"
+#include "y4_pt_tex.cuh"
 
 struct Y4PtWave
 {
@@ -171,6 +172,11 @@ Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
 	v.sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
 	v.m = sc.mats[v.sp.mat];
+	if(v.m.layer_count > 0)          // initBsdf evaluates the node chain; getShaderColor / emit() read it (material_shiny_diffuse.cc:237,244)
+	{
+		v.m.color = y4_diffuse_shader_color(sc, v.m, v.sp, h.bu, h.bv, h.prim);
+		v.m.emit = cscale(v.m.color, v.m.emit_strength);
+	}
 	v.wo = xneg(d);
 	return v;
 }

@@ -47,6 +47,27 @@ struct Y4PtMaterial
 	int is_diffuse;
 	int oren_nayar; float oren_a, oren_b;
 	int double_sided, receive_shadows, flat_material;
+	int layer_first, layer_count;   // diffuse_shader chain in Y4PtScene::layers (0 layers: plain colour)
+	float emit_strength;            // emit() with a diffuse_shader: shader colour * emit_strength_
+};
+
+// ImageTexture state (texture_image.cc:476-597) + texels as Image::getColor returns them
+struct Y4PtTexture
+{
+	const float4 *texels;
+	int w, h, clip, interp;
+	int xrepeat, yrepeat, mirror_x, mirror_y, rot90;
+	int cropx, cropy; float cropminx, cropmaxx, cropminy, cropmaxy;
+	int checker_even, checker_odd; float checker_dist;
+	int adjustments_set, adj_clamp; float adj_intensity, adj_contrast, adj_red, adj_green, adj_blue;
+};
+// TextureMapperNode + LayerNode state of one layer of a diffuse_shader chain
+struct Y4PtLayer
+{
+	int tex, coords, projection, map_x, map_y, map_z;
+	V3 scale, offset;               // offset already doubled (shader_node_basic.cc:361)
+	uint32_t flags; int blend, do_color; float colfac;
+	float def_col[4], upper_col[4];
 };
 
 struct Y4PtLight
@@ -93,6 +114,8 @@ struct Y4PtScene
 	const Y4PtMaterial *mats;       // [n_mats]
 	const float4 *tri_shade;        // [n_tri] geometric normal (xyz) + material index (w, as int bits), see y4_tri_shade
 	const float *normals;           // [n_tri * 9] exported vertex normals or null
+	const Y4PtTexture *textures; const Y4PtLayer *layers;     // diffuse_shader chains (y4_pt_tex.cuh) or null
+	const float *tri_orco, *tri_uv; // [n_tri * 9] orco points / [n_tri * 6] uv values per triangle, or null
 	Y4LdsTables lds;                // Faure tables (device pointers)
 };
 

@@ -7,9 +7,10 @@ same names without the prefix, same argument order and meaning) -> Interface
 `paramsSet*` / `paramsClearAll` / `create*` are kept (interface.cc:118-197).  What the reference
 would render with `scene_accelerator = <kd-tree>` + `type = pathtracing` on CPU threads is rendered
 here by the BVH8 accelerator + wavefront path tracer kernels.  Scene features outside the supported
-set (shinydiffusemat without mirror/transparency/nodes, light_mat, pointlight,
-arealight, perspective pinhole camera, constant background, pathtracing) raise Y4Error -- they are
-never approximated, and there is no CPU fallback.
+set (shinydiffusemat without mirror/transparency, with an optional `diffuse_shader`
+chain of layer + texture_mapper nodes over image textures; light_mat; point/area/directional/sun/sphere/
+spot lights; perspective camera; constant background; pathtracing / directlighting) raise Y4Error --
+they are never approximated, and there is no CPU fallback.
 """
 from __future__ import annotations
 
@@ -18,7 +19,7 @@ from typing import Dict, List, Optional
 
 import numpy as np
 
-from . import _lib
+from . import _lib, images
 from ._lib import Y4Error
 from .accelerator import ACCELERATOR_TYPE, AcceleratorB200
 
@@ -33,6 +34,9 @@ class _Mesh:
         self.normals: List[tuple] = []
         self.tris: List[tuple] = []
         self.tri_mats: List[str] = []
+        self.orco: List[tuple] = []        # addVertexWithOrco (MeshObject::orco_points_)
+        self.uvs: List[tuple] = []         # addUv (MeshObject::uv_values_)
+        self.tri_uvs: List[tuple] = []     # uv indices per face (addTriangleWithUv), None for addTriangle
         self.visibility = params.get("visibility", "normal")
         self.is_base = bool(params.get("is_base_object", False))
         self.instance_of: Optional[str] = None
@@ -45,6 +49,12 @@ class Interface:
     def __init__(self, device: int = 0, shard_index: int = 0, shard_count: int = 1):
         self.device, self.shard_index, self.shard_count = device, shard_index, shard_count
         self.params: Dict[str, object] = {}
+        self.eparams: List[Dict[str, object]] = []     # the ParamMap list of paramsPushList (shader nodes)
+        self._cparams = self.params
+        self.images: Dict[str, np.ndarray] = {}        # createImage: decoded texels [h, w, 4]
+        self.textures: Dict[str, dict] = {}
+        self.image_dir = "."                           # relative image file names resolve against this directory
+        self.warnings: List[str] = []
         self.materials: Dict[str, dict] = {}
         self.lights: Dict[str, dict] = {}
         self.cameras: Dict[str, dict] = {}
@@ -64,32 +74,106 @@ class Interface:
     # ---- the "current ParamMap" (interface.cc:118-181) -------------------------------------------
     def paramsClearAll(self):
         self.params = {}
+        self.eparams = []
+        self._cparams = self.params
 
     def paramsSetString(self, name, s):
-        self.params[name] = str(s)
+        self._cparams[name] = str(s)
 
     def paramsSetBool(self, name, b):
-        self.params[name] = bool(b)
+        self._cparams[name] = bool(b)
 
     def paramsSetInt(self, name, i):
-        self.params[name] = int(i)
+        self._cparams[name] = int(i)
 
     def paramsSetFloat(self, name, f):
-        self.params[name] = float(f)
+        self._cparams[name] = float(f)
 
     def paramsSetVector(self, name, x, y, z):
-        self.params[name] = (float(x), float(y), float(z))
+        self._cparams[name] = (float(x), float(y), float(z))
 
     def paramsSetColor(self, name, r, g, b, a=1.0):
-        self.params[name] = (float(r), float(g), float(b), float(a))
+        self._cparams[name] = (float(r), float(g), float(b), float(a))
 
     def paramsPushList(self):
-        raise Y4Error("shader-node parameter lists (paramsPushList) are not supported by the GPU back end")
+        """Interface::paramsPushList (interface.cc:183-187): later paramsSet* calls fill a new ParamMap of the node list."""
+        self.eparams.append({})
+        self._cparams = self.eparams[-1]
 
     def paramsEndList(self):
-        pass
+        self._cparams = self.params
 
     # ---- object factories (scene.cc:363-526) ------------------------------------------------------
+    def createImage(self, name):
+        """Scene::createImage -> Image::factory (image.cc:38-101).  A file the reference build cannot load leaves no
+        image behind (False); textures and node materials that need it are then dropped like in the reference."""
+        try:
+            self.images[name] = images.load_image(dict(self.params), self.image_dir)
+        except images.ImageLoadError as exc:
+            self.warnings.append(f"image '{name}': {exc}")
+            return False
+        return True
+
+    def createTexture(self, name):
+        """Scene::createTexture -> ImageTexture::factory (texture_image.cc:476-597)."""
+        p = dict(self.params)
+        if p.get("type") != "image":
+            raise Y4Error(f"texture type '{p.get('type')}' is not supported by the GPU back end (image textures only)")
+        if p.get("image_name", "") not in self.images:
+            self.warnings.append(f"texture '{name}': image '{p.get('image_name', '')}' does not exist, dropping texture")
+            return False
+        interp = str(p.get("interpolate", ""))
+        if interp in ("bicubic", "mipmap_trilinear", "mipmap_ewa"):
+            raise Y4Error(f"texture '{name}': interpolate '{interp}' is not supported by the GPU back end (none / bilinear)")
+        if float(p.get("adj_saturation", 1.0)) != 1.0 or float(p.get("adj_hue", 0.0)) != 0.0:
+            raise Y4Error(f"texture '{name}': hue / saturation adjustments are not supported by the GPU back end")
+        if p.get("normalmap", False):
+            raise Y4Error(f"texture '{name}': normal maps are not supported by the GPU back end")
+        self.textures[name] = p
+        return True
+
+    def _diffuse_chain(self, name, p, node_params):
+        """NodeMaterial::loadNodes / parseNodes (material_node.cc:102-187) for the `diffuse_shader` slot -> the chain of
+        (layer params, texture_mapper params) pairs, bottom layer first; None when the reference would drop the nodes."""
+        nodes = {}
+        for n in node_params:
+            if n.get("element", "shader_node") != "shader_node":
+                continue
+            if "name" not in n or n["name"] in nodes or "type" not in n:
+                self.warnings.append(f"material '{name}': unnamed / duplicate / untyped shader node, nodes dropped")
+                return None
+            if n["type"] not in ("layer", "texture_mapper"):
+                raise Y4Error(f"material '{name}': shader node type '{n['type']}' is not supported by the GPU back end")
+            if n["type"] == "texture_mapper" and n.get("texture", "") not in self.textures:
+                self.warnings.append(f"material '{name}': texture '{n.get('texture', '')}' does not exist, nodes dropped")
+                return None           # TextureMapperNode::factory returns nullptr -> loadNodes clears the table
+            nodes[n["name"]] = n
+        for n in nodes.values():       # configInputs (shader_node_layer.cc:156-190)
+            if n["type"] == "layer" and (n.get("input") not in nodes or ("upper_layer" in n and n["upper_layer"] not in nodes)):
+                self.warnings.append(f"material '{name}': layer node '{n['name']}' has no input, nodes dropped")
+                return None
+        root = nodes.get(p["diffuse_shader"])
+        if root is None:
+            self.warnings.append(f"material '{name}': shader node '{p['diffuse_shader']}' does not exist")
+            return None
+        chain, n, seen = [], root, set()
+        while n is not None:
+            if n["type"] != "layer" or n["name"] in seen:
+                raise Y4Error(f"material '{name}': the diffuse_shader must be a stack of layer nodes")
+            seen.add(n["name"])
+            mapper = nodes[n["input"]]
+            if mapper["type"] != "texture_mapper":
+                raise Y4Error(f"material '{name}': layer inputs other than texture_mapper nodes are not supported by the GPU back end")
+            if not n.get("color_input", True):
+                raise Y4Error(f"material '{name}': scalar layer inputs are not supported by the GPU back end")
+            if mapper.get("texco", "global") in ("transformed", "window", "normal"):
+                raise Y4Error(f"material '{name}': texco '{mapper.get('texco')}' is not supported by the GPU back end")
+            if mapper.get("mapping", "plain") in ("tube", "sphere"):
+                raise Y4Error(f"material '{name}': mapping '{mapper.get('mapping')}' is not supported by the GPU back end")
+            chain.insert(0, (n, mapper))
+            n = nodes[n["upper_layer"]] if "upper_layer" in n else None
+        return chain
+
     def createMaterial(self, name):
         p = dict(self.params)
         t = p.get("type")
@@ -99,9 +183,13 @@ class Interface:
                     raise Y4Error(f"shinydiffusemat '{name}': {k} != 0 is not supported by the GPU back end")
             if p.get("fresnel_effect", False):
                 raise Y4Error(f"shinydiffusemat '{name}': fresnel_effect is not supported by the GPU back end")
+            if float(p.get("wireframe_amount", 0.0)) != 0.0:
+                raise Y4Error(f"shinydiffusemat '{name}': wireframe shading is not supported by the GPU back end")
             for k in p:
-                if k.endswith("_shader"):
-                    raise Y4Error(f"shinydiffusemat '{name}': shader nodes are not supported by the GPU back end")
+                if k.endswith("_shader") and k != "diffuse_shader":
+                    raise Y4Error(f"shinydiffusemat '{name}': shader slot '{k}' is not supported by the GPU back end (diffuse_shader only)")
+            if "diffuse_shader" in p:
+                p["_diffuse_chain"] = self._diffuse_chain(name, p, [dict(e) for e in self.eparams])
         elif t != "light_mat":
             raise Y4Error(f"material type '{t}' is not supported by the GPU back end")
         self.materials[name] = p
@@ -184,12 +272,26 @@ class Interface:
         self._cur.verts.append((x, y, z))
         return len(self._cur.verts) - 1
 
+    def addVertexWithOrco(self, x, y, z, ox, oy, oz):
+        self._cur.orco.append((ox, oy, oz))
+        return self.addVertex(x, y, z)
+
+    def addUv(self, u, v):
+        self._cur.uvs.append((u, v))
+        return len(self._cur.uvs) - 1
+
+    def addTriangleWithUv(self, a, b, c, uv_a, uv_b, uv_c):
+        self.addTriangle(a, b, c)
+        self._cur.tri_uvs[-1] = (uv_a, uv_b, uv_c)
+        return True
+
     def addNormal(self, x, y, z):
         self._cur.normals.append((x, y, z))
 
     def addTriangle(self, a, b, c):
         self._cur.tris.append((a, b, c))
         self._cur.tri_mats.append(self._cur_mat)
+        self._cur.tri_uvs.append(None)
         return True
 
     def add_mesh_arrays(self, verts: np.ndarray, tris: np.ndarray):
@@ -199,6 +301,7 @@ class Interface:
         for t in np.asarray(tris, np.int64).reshape(-1, 3):
             self._cur.tris.append((base + int(t[0]), base + int(t[1]), base + int(t[2])))
             self._cur.tri_mats.append(self._cur_mat)
+            self._cur.tri_uvs.append(None)
 
     def endObject(self):
         self._cur = None
@@ -230,19 +333,21 @@ class Interface:
         mat_names = list(self.materials)
         mat_index = {n: i for i, n in enumerate(mat_names)}
         tris, flags, normals, any_normals = [], [], [], False
+        textured = any(m.get("_diffuse_chain") for m in self.materials.values())
+        orcos, uvs = [], []
         base_cache: Dict[str, tuple] = {}      # per mesh: fp32 vertices, index array, flag words, normals (shared by its instances)
 
         def mesh_arrays(base: _Mesh):
             if base.name in base_cache:
                 return base_cache[base.name]
-            vis_o, sh_o = VIS[base.visibility]
+            vis_o, sh_o = VIS.get(base.visibility, VIS["normal"])
             v = np.asarray(base.verts, np.float64).astype(np.float32)  # API doubles are narrowed to float (interface.cc:87)
             idx = np.asarray(base.tris, np.int64)
             words = {}
             for mn in set(base.tri_mats):
                 if mn is None:
                     raise Y4Error(f"object '{base.name}': triangle without a material")
-                vis_m, sh_m = VIS[self.materials[mn].get("visibility", "normal")]
+                vis_m, sh_m = VIS.get(self.materials[mn].get("visibility", "normal"), VIS["normal"])
                 w = (mat_index[mn] << _lib.TRI_MAT_SHIFT)
                 if vis_o and vis_m:
                     w |= _lib.TRI_VIS_CLOSEST
@@ -255,18 +360,30 @@ class Interface:
             nn = None
             if base.normals and len(base.normals) == len(base.verts):
                 nn = np.asarray(base.normals, np.float64).astype(np.float32)[idx].reshape(-1, 9)
-            base_cache[base.name] = (v, idx, f, nn)
+            oc = uv = None
+            if textured:
+                if base.orco and len(base.orco) == len(base.verts):      # MeshObject::hasOrco
+                    oc = np.asarray(base.orco, np.float64).astype(np.float32)[idx].reshape(-1, 9)
+                if base.uvs and any(t is not None for t in base.tri_uvs):
+                    uva = np.asarray(base.uvs, np.float64).astype(np.float32)
+                    if any(t is None for t in base.tri_uvs):
+                        raise Y4Error(f"object '{base.name}': faces with and without uv indices in one mesh are not supported")
+                    uv = uva[np.asarray(base.tri_uvs, np.int64)].reshape(-1, 6)
+            base_cache[base.name] = (v, idx, f, nn, oc, uv)
             return base_cache[base.name]
 
         for name in sorted(self.objects):
             o = self.objects[name]
             base = self.objects[o.instance_of] if o.instance_of else o
-            vis_o, sh_o = VIS[base.visibility]
+            vis_o, sh_o = VIS.get(base.visibility, VIS["normal"])
             if (not vis_o and not sh_o) or o.is_base:
                 continue
             if not base.tris:
                 continue
-            v, idx, f, nn = mesh_arrays(base)
+            v, idx, f, nn, oc, uv = mesh_arrays(base)
+            if textured:      # NaN in the first float: no orco points / uv values on this mesh (see include/y4gpu.h)
+                orcos.append(oc if oc is not None else np.full((len(idx), 9), np.nan, np.float32))
+                uvs.append(uv if uv is not None else np.full((len(idx), 6), np.nan, np.float32))
             if o.instance_of:  # Matrix4 * Point3 in fp32, matrix4.h:85-90
                 m = o.matrix
                 v = np.stack([((m[r, 0] * v[:, 0] + m[r, 1] * v[:, 1]) + m[r, 2] * v[:, 2]) + m[r, 3] for r in range(3)], -1).astype(np.float32)
@@ -303,9 +420,59 @@ class Interface:
         cam.aperture, cam.dof_distance = float(cam_p.get("aperture", 0.0)), float(cam_p.get("dof_distance", 0.0))
         cam.near_clip, cam.far_clip = float(cam_p.get("nearClip", 0.0)), float(cam_p.get("farClip", -1.0))
 
+        # textures + layer chains of the diffuse_shader slots (only the textures some chain uses are uploaded)
+        tex_index: Dict[str, int] = {}
+        tex_list, layer_list, chain_of = [], [], {}
+        for n in mat_names:
+            chain = self.materials[n].get("_diffuse_chain")
+            if not chain:
+                continue
+            chain_of[n] = (len(layer_list), len(chain))
+            for li, (lay, mapper) in enumerate(chain):
+                tname = mapper["texture"]
+                if tname not in tex_index:
+                    tex_index[tname] = len(tex_list)
+                    tex_list.append(tname)
+                L = _lib.PtLayer()
+                L.texture = tex_index[tname]
+                L.texco = _lib.TEXCO.get(str(mapper.get("texco", "global")), 0)
+                # the projection applies to discrete (image) textures only; unknown names leave Plain (shader_node_basic.cc:343-349)
+                L.mapping = _lib.PROJECTIONS.get(str(mapper.get("mapping", "plain")), 0)
+                L.proj_x, L.proj_y, L.proj_z = int(mapper.get("proj_x", 1)), int(mapper.get("proj_y", 2)), int(mapper.get("proj_z", 3))
+                L.scale[:] = mapper.get("scale", (1.0, 1.0, 1.0))
+                L.offset[:] = mapper.get("offset", (0.0, 0.0, 0.0))
+                L.flags = (_lib.LAYER_RGB_TO_INT if lay.get("noRGB", False) else 0) | (_lib.LAYER_STENCIL if lay.get("stencil", False) else 0) \
+                    | (_lib.LAYER_NEGATIVE if lay.get("negative", False) else 0)
+                L.blend_mode = _lib.BLEND_MODES.get(str(lay.get("blend_mode", "mix")), 0)
+                L.do_color, L.colfac = int(bool(lay.get("do_color", True))), float(lay.get("colfac", 1.0))
+                L.def_col[:] = lay.get("def_col", (1.0, 1.0, 1.0, 1.0))[:3]
+                if li == 0:
+                    L.upper_color[:] = lay.get("upper_color", (0.0, 0.0, 0.0, 0.0))
+                layer_list.append(L)
+        textures = (_lib.PtTexture * max(1, len(tex_list)))()
+        texel_arrays = []
+        for i, tname in enumerate(tex_list):
+            tp, TS = self.textures[tname], textures[i]
+            tx = self.images[tp["image_name"]]
+            texel_arrays.append(tx)
+            TS.texels, TS.height, TS.width = tx.ctypes.data, tx.shape[0], tx.shape[1]
+            TS.clip = _lib.CLIP_MODES.get(str(tp.get("clipping", "")), _lib.CLIP_MODES["repeat"])
+            TS.interpolate = _lib.INTERPOLATIONS.get(str(tp.get("interpolate", "")), _lib.INTERPOLATIONS["bilinear"])
+            TS.xrepeat, TS.yrepeat = int(tp.get("xrepeat", 1)), int(tp.get("yrepeat", 1))
+            TS.mirror_x, TS.mirror_y, TS.rot90 = int(bool(tp.get("mirror_x", False))), int(bool(tp.get("mirror_y", False))), int(bool(tp.get("rot90", False)))
+            TS.cropmin_x, TS.cropmin_y = float(tp.get("cropmin_x", 0.0)), float(tp.get("cropmin_y", 0.0))
+            TS.cropmax_x, TS.cropmax_y = float(tp.get("cropmax_x", 1.0)), float(tp.get("cropmax_y", 1.0))
+            TS.even_tiles, TS.odd_tiles, TS.checker_dist = int(bool(tp.get("even_tiles", False))), int(bool(tp.get("odd_tiles", True))), float(tp.get("checker_dist", 0.0))
+            TS.adj_intensity, TS.adj_contrast = float(tp.get("adj_intensity", 1.0)), float(tp.get("adj_contrast", 1.0))
+            TS.adj_mult_factor_red, TS.adj_mult_factor_green, TS.adj_mult_factor_blue = (float(tp.get("adj_mult_factor_" + c, 1.0)) for c in ("red", "green", "blue"))
+            TS.adj_clamp = int(bool(tp.get("adj_clamp", False)))
+        layers = (_lib.PtLayer * max(1, len(layer_list)))(*layer_list)
+
         mats = (_lib.PtMaterial * max(1, len(mat_names)))()
         for i, n in enumerate(mat_names):
             p, m = self.materials[n], mats[i]
+            if n in chain_of:
+                m.layer_first, m.layer_count = chain_of[n]
             m.color[:] = p.get("color", (1.0, 1.0, 1.0, 1.0))[:3]
             m.receive_shadows, m.flat_material = int(p.get("receive_shadows", True)), int(p.get("flat_material", False))
             if p["type"] == "light_mat":
@@ -376,8 +543,11 @@ class Interface:
         pr.rr_seed = int(rp.get("b200_rr_seed", 0x5EED)) & 0xFFFFFFFF
         pr.wave_size = int(rp.get("b200_wave_size", 0))
         pr.profile = int(rp.get("b200_profile", 0))
+        tri_orco = np.ascontiguousarray(np.concatenate(orcos), np.float32) if layer_list and orcos else None
+        tri_uv = np.ascontiguousarray(np.concatenate(uvs), np.float32) if layer_list and uvs else None
         return {"tris": T, "flags": F, "normals": N, "cam": cam, "mats": mats, "n_mat": len(mat_names), "lights": lights,
-                "n_light": len(light_names), "params": pr}
+                "n_light": len(light_names), "params": pr, "textures": textures, "n_tex": len(tex_list), "layers": layers,
+                "n_layers": len(layer_list), "tri_orco": tri_orco, "tri_uv": tri_uv, "_texels": texel_arrays}
 
     # ---- render (Scene::render -> TiledIntegrator::render, integrator_tiled.cc:97-233) --------------
     def upload(self):
@@ -389,6 +559,9 @@ class Interface:
             self.accelerator = AcceleratorB200(a["tris"], flags=a["flags"], device=self.device)
         L, ctx = self.accelerator._L, self.accelerator.ctx
         nptr = C.c_void_p(a["normals"].ctypes.data) if a["normals"] is not None else None
+        optr = C.c_void_p(a["tri_orco"].ctypes.data) if a["tri_orco"] is not None else None
+        uptr = C.c_void_p(a["tri_uv"].ctypes.data) if a["tri_uv"] is not None else None
+        _lib.check(ctx, L.y4gpu_pt_set_textures(ctx, a["textures"], a["n_tex"], a["layers"], a["n_layers"], optr, uptr), "y4gpu_pt_set_textures")
         _lib.check(ctx, L.y4gpu_pt_set_scene(ctx, C.byref(a["cam"]), a["mats"], a["n_mat"], a["lights"], a["n_light"], C.byref(a["params"]), nptr), "y4gpu_pt_set_scene")
         if self.film_buffers is not None:
             w, rgba = self.film_buffers

@@ -363,6 +363,185 @@ def city(api, n_tri_target=10_000_000, width=3840, height=2160, spp=16, bounces=
     return total
 
 
+# ---- C1: the reference's tests/test01 scene ---------------------------------------------------------------
+# Six textured cubes on a plane, one point light, constant background (tests/test01/test01.c of the reference:
+# geometry :660-860, materials :268-650, light :652-663, camera :862-875, render parameters :896-960).  Each cube has
+# orco points -1..1 and a shinydiffusemat whose diffuse_shader is a `layer` (mix) over a cube-mapped `texture_mapper`
+# on an image texture; the six textures are one picture in six file formats.
+TEST01_CUBES = [    # object, material, image file, colour space, x range, y range, diffuse_reflect, layer colfac
+    ("Cube.005", "Material.008", "Texture.005", "tex.tif", "sRGB", (-4.40469, -2.40468), (1.44162, 3.44162), 0.5, 1.0),
+    ("Cube.004", "Material.007", "Texture.004", "tex.tga", "sRGB", (3.26859, 5.26859), (-0.393062, 1.60694), 1.0, 1.0),
+    ("Cube.003", "Material.006", "Texture.003", "tex.png", "sRGB", (-0.635578, 1.36442), (3.54144, 5.54144), 0.6, 1.0),
+    ("Cube.002", "Material.005", "Texture.002", "tex.jpg", "sRGB", (-0.635578, 1.36442), (-0.393062, 1.60694), 0.4, 1.0),
+    ("Cube.001", "Material.004", "Texture.001", "tex.hdr", "LinearRGB", (-0.635578, 1.36442), (-3.81854, -1.81854), 1.0, 0.95),
+    ("Cube", "Material.003", "Texture", "tex.exr", "LinearRGB", (-5.01096, -3.01096), (-1.94285, 0.0571451), 1.0, 0.95),
+]
+TEST01_CUBE_TRIS = [(2, 0, 1), (2, 1, 3), (3, 7, 6), (3, 6, 2), (7, 5, 4), (7, 4, 6), (0, 4, 5), (0, 5, 1), (0, 2, 6), (0, 6, 4), (5, 7, 3), (5, 3, 1)]
+
+
+def _set_params(api, extra):
+    """Extra parameters of a scene variant: str / bool / int / float / 3-tuple (vector) / 4-tuple (colour)."""
+    for k, v in (extra or {}).items():
+        if isinstance(v, str):
+            api.paramsSetString(k, v)
+        elif isinstance(v, bool):
+            api.paramsSetBool(k, v)
+        elif isinstance(v, int):
+            api.paramsSetInt(k, v)
+        elif isinstance(v, float):
+            api.paramsSetFloat(k, v)
+        elif len(v) == 3:
+            api.paramsSetVector(k, float(v[0]), float(v[1]), float(v[2]))
+        else:
+            api.paramsSetColor(k, float(v[0]), float(v[1]), float(v[2]), float(v[3]))
+
+
+def test01(api, width=480, height=270, spp=3, integrator="pathtracing", bounces=4, path_samples=1, filter_type="gauss", aa_pixelwidth=1.5,
+           accelerator="yafaray-kdtree-original", threads=1, texture_extra=None, mapper_extra=None, layer_extra=None, with_uv=False):
+    """tests/test01 with the integrator of BASELINE config 1 (`pathtracing`; the shipped file uses `directlighting`, which
+    `integrator="directlighting"` selects).  Image files are looked up relative to the renderer's working / image directory."""
+    for _, _, tex, fname, cspace, _, _, _, _ in TEST01_CUBES:
+        api.paramsClearAll()
+        api.paramsSetString("type", "image")       # as in test01.c (not an Image::Type name; the loader picks the type)
+        api.paramsSetString("filename", fname)
+        api.paramsSetString("color_space", cspace)
+        api.paramsSetFloat("gamma", 1.0)
+        api.paramsSetString("image_optimization", "optimized")
+        api.createImage(tex + "_image")
+        api.paramsClearAll()
+        api.paramsSetString("type", "image")
+        api.paramsSetString("image_name", tex + "_image")
+        _set_params(api, texture_extra)
+        api.createTexture(tex)
+    _material(api, "defaultMat", (0.8, 0.8, 0.8))
+    for _, mat, tex, _, _, _, _, diffuse_reflect, colfac in TEST01_CUBES:
+        api.paramsClearAll()
+        api.paramsSetString("type", "shinydiffusemat")
+        api.paramsSetColor("color", 0.8, 0.8, 0.8, 1.0)
+        api.paramsSetFloat("diffuse_reflect", diffuse_reflect)
+        api.paramsSetString("diffuse_shader", "diff_layer0")
+        api.paramsPushList()
+        api.paramsSetString("element", "shader_node")
+        api.paramsSetString("type", "layer")
+        api.paramsSetString("name", "diff_layer0")
+        api.paramsSetString("input", "map0")
+        api.paramsSetString("blend_mode", "mix")
+        api.paramsSetFloat("colfac", colfac)
+        api.paramsSetBool("color_input", True)
+        api.paramsSetColor("def_col", 1.0, 0.0, 1.0, 1.0)
+        api.paramsSetBool("do_color", True)
+        api.paramsSetBool("do_scalar", False)
+        api.paramsSetColor("upper_color", 0.8, 0.8, 0.8, 1.0)
+        api.paramsSetFloat("upper_value", 0.0)
+        _set_params(api, layer_extra)
+        api.paramsPushList()
+        api.paramsSetString("element", "shader_node")
+        api.paramsSetString("type", "texture_mapper")
+        api.paramsSetString("name", "map0")
+        api.paramsSetString("texture", tex)
+        api.paramsSetString("texco", "orco")
+        api.paramsSetString("mapping", "cube")
+        api.paramsSetInt("proj_x", 1)
+        api.paramsSetInt("proj_y", 2)
+        api.paramsSetInt("proj_z", 3)
+        api.paramsSetVector("scale", 1.0, 1.0, 1.0)
+        api.paramsSetVector("offset", 0.0, 0.0, 0.0)
+        _set_params(api, mapper_extra)
+        api.paramsEndList()
+        api.createMaterial(mat)
+    _material(api, "Material.002", (0.8, 0.8, 0.8))
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "pointlight")
+    api.paramsSetColor("color", 1.0, 1.0, 1.0, 1.0)
+    api.paramsSetVector("from", 5.27648, -4.88993, 8.89514)
+    api.paramsSetFloat("power", 72.0)
+    api.createLight("Point")
+
+    for obj, mat, _, _, _, xr, yr, _, _ in TEST01_CUBES:
+        api.paramsClearAll()
+        api.paramsSetString("type", "mesh")
+        api.paramsSetBool("has_orco", True)
+        api.paramsSetBool("has_uv", bool(with_uv))
+        api.paramsSetInt("num_vertices", 8)
+        api.paramsSetInt("num_faces", 6)
+        api.createObject(obj)
+        for ix in (0, 1):
+            for iy in (0, 1):
+                for iz in (0, 1):
+                    api.addVertexWithOrco(xr[ix], yr[iy], (1.00136e-05, 2.00001)[iz], 2.0 * ix - 1.0, 2.0 * iy - 1.0, 2.0 * iz - 1.0)
+        api.setCurrentMaterial(mat)
+        if with_uv:         # variant for the uv texture coordinates: one uv value per cube corner
+            for k in range(8):
+                api.addUv(0.25 * (k % 4) + 0.1 * (k // 4), 0.35 * (k // 2) - 0.2 * (k % 2))
+        for t in TEST01_CUBE_TRIS:
+            if with_uv:
+                api.addTriangleWithUv(t[0], t[1], t[2], t[0], t[1], t[2])
+            else:
+                api.addTriangle(*t)
+        api.endObject()
+    _mesh(api, "Plane", "Material.002", [(-10.0, -10.0, 0.0), (10.0, -10.0, 0.0), (-10.0, 10.0, 0.0), (10.0, 10.0, 0.0)], [(0, 1, 3), (0, 3, 2)])
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "perspective")
+    api.paramsSetVector("from", 8.64791, -7.22615, 8.1295)
+    api.paramsSetVector("to", 8.03447, -6.65603, 7.58301)
+    api.paramsSetVector("up", 8.25644, -6.8447, 8.9669)
+    api.paramsSetInt("resx", width)
+    api.paramsSetInt("resy", height)
+    api.paramsSetFloat("focal", 1.09375)
+    api.createCamera("Camera")
+
+    api.paramsClearAll()
+    api.paramsSetString("camera_name", "Camera")
+    api.createRenderView("view")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "constant")
+    api.paramsSetColor("color", 0.7, 0.7, 0.7, 1.0)
+    api.paramsSetFloat("power", 0.5)
+    api.paramsSetBool("ibl", False)
+    api.createBackground("world_background")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", integrator)
+    api.paramsSetInt("raydepth", 2)
+    api.paramsSetInt("shadowDepth", 2)
+    api.paramsSetBool("transpShad", False)
+    api.paramsSetBool("caustics", False)
+    api.paramsSetString("caustic_type", "none")
+    api.paramsSetBool("do_AO", False)
+    if integrator == "pathtracing":
+        api.paramsSetInt("bounces", bounces)
+        api.paramsSetInt("path_samples", path_samples)
+        api.paramsSetInt("russian_roulette_min_bounces", bounces)
+    api.createIntegrator("default")
+
+    api.paramsClearAll()
+    api.paramsSetString("type", "combined")
+    api.paramsSetString("image_type", "ColorAlpha")
+    api.paramsSetString("exported_image_type", "ColorAlpha")
+    api.paramsSetString("exported_image_name", "Combined")
+    api.defineLayer()
+
+    api.paramsClearAll()
+    api.paramsSetString("integrator_name", "default")
+    api.paramsSetString("background_name", "world_background")
+    api.paramsSetString("scene_accelerator", accelerator)
+    api.paramsSetInt("width", width)
+    api.paramsSetInt("height", height)
+    api.paramsSetInt("threads", threads)
+    api.paramsSetInt("AA_passes", 1)
+    api.paramsSetInt("AA_minsamples", spp)
+    api.paramsSetInt("AA_inc_samples", 1)
+    api.paramsSetFloat("AA_pixelwidth", aa_pixelwidth)
+    api.paramsSetFloat("AA_threshold", 0.05)
+    api.paramsSetString("filter_type", filter_type)
+    api.paramsSetString("tiles_order", "linear")
+    api.paramsSetInt("tile_size", 32)
+    api.setupRender()
+
+
 def build(api, scene="cornell", **kw):
     """Dispatch by scene name (the committed golden configurations carry a `scene` key)."""
-    return {"cornell": cornell_box, "city": city}[scene](api, **kw)
+    return {"cornell": cornell_box, "city": city, "test01": test01}[scene](api, **kw)

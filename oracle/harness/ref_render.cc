@@ -11,6 +11,7 @@
 //     createMaterial|createLight|createCamera|createBackground|createIntegrator|createRenderView|createObject|createOutput name
 //     defineLayer | startGeometry | endGeometry | endObject | setCurrentMaterial name
 //     addVertex x y z | addNormal x y z | addTriangle a b c | smoothMesh name angle
+//     addVertexWithOrco x y z ox oy oz | addUv u v | addTriangleWithUv a b c ua ub uc | createImage name | createTexture name
 //     loadMesh file   (binary: int32 n_vert, int32 n_tri, float32 verts[n_vert*3], int32 tris[n_tri*3] -> addVertex/addTriangle)
 //     addInstance base 16 floats | setupRender
 //     render out.f32  (renders; the Combined layer arrives through the put-pixel callback as float
@@ -85,6 +86,8 @@ int main(int argc, char **argv)
 		else if(cmd == "createIntegrator") { ss >> a; yafaray_createIntegrator(yi, a.c_str()); }
 		else if(cmd == "createRenderView") { ss >> a; yafaray_createRenderView(yi, a.c_str()); }
 		else if(cmd == "createObject") { ss >> a; yafaray_createObject(yi, a.c_str()); }
+		else if(cmd == "createImage") { ss >> a; yafaray_createImage(yi, a.c_str()); }
+		else if(cmd == "createTexture") { ss >> a; yafaray_createTexture(yi, a.c_str()); }
 		else if(cmd == "createOutput") { ss >> a; yafaray_createOutput(yi, a.c_str()); }
 		else if(cmd == "defineLayer") yafaray_defineLayer(yi);
 		else if(cmd == "startGeometry") yafaray_startGeometry(yi);
@@ -92,6 +95,9 @@ int main(int argc, char **argv)
 		else if(cmd == "endObject") yafaray_endObject(yi);
 		else if(cmd == "setCurrentMaterial") { ss >> a; yafaray_setCurrentMaterial(yi, a.c_str()); }
 		else if(cmd == "addVertex") { double x, y, z; ss >> x >> y >> z; yafaray_addVertex(yi, x, y, z); }
+		else if(cmd == "addVertexWithOrco") { double x, y, z, ox, oy, oz; ss >> x >> y >> z >> ox >> oy >> oz; yafaray_addVertexWithOrco(yi, x, y, z, ox, oy, oz); }
+		else if(cmd == "addUv") { float u, v; ss >> u >> v; yafaray_addUv(yi, u, v); }
+		else if(cmd == "addTriangleWithUv") { int i, j, k, ui, uj, uk; ss >> i >> j >> k >> ui >> uj >> uk; yafaray_addTriangleWithUv(yi, i, j, k, ui, uj, uk); }
 		else if(cmd == "addNormal") { double x, y, z; ss >> x >> y >> z; yafaray_addNormal(yi, x, y, z); }
 		else if(cmd == "addTriangle") { int i, j, k; ss >> i >> j >> k; yafaray_addTriangle(yi, i, j, k); }
 		else if(cmd == "smoothMesh") { double ang; ss >> a >> ang; yafaray_smoothMesh(yi, a.c_str(), ang); }

@@ -88,15 +88,16 @@ class ScriptRecorder:
         return call
 
 
-def ref_render(recorder, env=None):
-    """Render a recorded scene with the UNMODIFIED reference -> (float32 [H, W, 4] linear RGBA, info)."""
+def ref_render(recorder, env=None, cwd=None):
+    """Render a recorded scene with the UNMODIFIED reference -> (float32 [H, W, 4] linear RGBA, info).
+    cwd: working directory of the renderer (relative image file names of textures resolve against it)."""
     with tempfile.TemporaryDirectory() as d:
         sp, op = os.path.join(d, "scene.script"), os.path.join(d, "out.f32")
         with open(sp, "w") as f:
             f.write("\n".join(recorder.lines) + f"\nrender {op}\n")
         e = dict(os.environ)
         e.update(env or {})
-        out = subprocess.run([os.path.join(REF_DIR, "ref_render"), sp], capture_output=True, text=True, check=True, env=e)
+        out = subprocess.run([os.path.join(REF_DIR, "ref_render"), sp], capture_output=True, text=True, check=True, env=e, cwd=cwd)
         info = json.loads(out.stdout.strip().splitlines()[-1])
         img = np.fromfile(op, np.float32).reshape(info["height"], info["width"], 4)
         return img, info

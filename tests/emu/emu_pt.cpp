@@ -76,6 +76,21 @@ static void push(uint32_t mask, uint32_t i, uint32_t n, std::vector<uint32_t> *p
 	if(path_q && (mask & Y4_PUSH_PATH)) path_q->push_back(i);
 }
 
+// textures of the next emu_pt_render calls (what y4gpu_pt_set_textures keeps in the context); texel memory stays the caller's
+static std::vector<Y4PtTexture> g_textures;
+static std::vector<Y4PtLayer> g_layers;
+static std::vector<float> g_tri_orco, g_tri_uv;
+extern "C" int emu_pt_set_textures(const y4gpu_pt_texture *textures, uint32_t n_tex, const y4gpu_pt_layer *layers, uint32_t n_layers,
+                                   const float *tri_orco, const float *tri_uv, uint64_t n_tri)
+{
+	g_textures.clear(); g_layers.clear(); g_tri_orco.clear(); g_tri_uv.clear();
+	for(uint32_t i = 0; i < n_tex; ++i) { Y4PtTexture t = derive_texture(textures[i]); t.texels = reinterpret_cast<const float4 *>(textures[i].texels); g_textures.push_back(t); }
+	for(uint32_t i = 0; i < n_layers; ++i) g_layers.push_back(derive_layer(layers[i]));
+	if(tri_orco && n_layers) g_tri_orco.assign(tri_orco, tri_orco + 9 * n_tri);
+	if(tri_uv && n_layers) g_tri_uv.assign(tri_uv, tri_uv + 6 * n_tri);
+	return 0;
+}
+
 extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material *mats, uint32_t n_mat, const y4gpu_pt_light *lights, uint32_t n_light,
                              const y4gpu_pt_params *params, const float *verts, const uint32_t *flags, int n_tri, const float *normals,
                              int n_samples, int offset, int aa_pass, int shard_index, int shard_count, float *film_w, float *film_rgba,
@@ -107,6 +122,8 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	std::vector<Y4PtMaterial> hm(n_mat);
 	for(uint32_t i = 0; i < n_mat; ++i) hm[i] = derive_material(mats[i]);
 	sc.lights = hl.data(); sc.mats = hm.data(); sc.tri_shade = tri_shade.data(); sc.normals = normals;
+	sc.textures = g_textures.empty() ? nullptr : g_textures.data(); sc.layers = g_layers.empty() ? nullptr : g_layers.data();
+	sc.tri_orco = g_tri_orco.empty() ? nullptr : g_tri_orco.data(); sc.tri_uv = g_tri_uv.empty() ? nullptr : g_tri_uv.data();
 	sc.lds.sigma = fh.sigma.data(); sc.lds.offset = fh.offset; sc.lds.prime = fh.prime; sc.lds.inv_prime = fh.inv_prime; sc.lds.sigma_d = fh.sigma_d.data(); sc.lds.magic = fh.magic;
 
 	// same pixel-sample enumeration as k_pt_fill (y4_pt.cu)

@@ -10,6 +10,7 @@ from /root/reference by `make -C oracle ref`).  Run in the build container only:
   pt_dof.npz         <- the same harness on the Cornell box with a lens (PT_GOLDEN_DOF)
   pt_lights.npz      <- the same harness on the Cornell box with directional / sun / sphere lights (PT_GOLDEN_LIGHTS)
   pt_city.npz        <- the same harness on scenes_pt.city (instanced buildings) for PT_GOLDEN_CITY
+  pt_test01.npz      <- the same harness on scenes_pt.test01 (the reference's tests/test01 scene: image textures) for PT_GOLDEN_TEST01
   pt_cornell.npz     <- oracle/_ref/ref_render (reference PathIntegrator + kd-tree through the C API,
                         threads=1, tiles linear) on scenes_pt.cornell_box for the PT_GOLDEN configurations
 """
@@ -56,21 +57,57 @@ PT_GOLDEN_LIGHTS = {
 }
 
 
-def make_extra(configs, filename):
+# C1 (BASELINE configs[0]): the reference's tests/test01 scene -- six cubes with image textures (layer + cube-mapped
+# texture_mapper nodes on orco coordinates) -- with the path tracer, as shipped (directlighting), and variants that walk
+# through the other texture / mapper / layer modes -> pt_test01.npz.  The reference build here has the TGA and HDR
+# loaders only (oracle/Makefile), so four of the six textures fail to load and their materials fall back to the plain
+# colour, in the reference and in the mirror alike.  The two image files it can load are copied next to the fixtures
+# (tests/golden/test01/: test input data of the reference's own test, needed where /root/reference does not exist).
+TEST01_DIR = os.path.join(HERE, "test01")
+PT_GOLDEN_TEST01 = {
+    "c1_test01_pathtracing": dict(scene="test01", width=480, height=270, spp=3, bounces=4),
+    "c1_test01_as_shipped_directlighting": dict(scene="test01", width=480, height=270, spp=3, integrator="directlighting"),
+    "tex_uv_repeat_mirror_adjust_multiply": dict(scene="test01", width=160, height=90, spp=2, bounces=3, with_uv=True,
+        texture_extra={"xrepeat": 3, "yrepeat": 2, "mirror_x": True, "mirror_y": True, "adj_intensity": 1.2, "adj_contrast": 0.8,
+                       "adj_mult_factor_red": 0.7, "adj_clamp": True},
+        mapper_extra={"texco": "uv", "mapping": "plain", "offset": (0.3, 0.1, 0.0)}, layer_extra={"blend_mode": "multiply", "colfac": 0.7}),
+    "tex_global_checker_nearest_stencil": dict(scene="test01", width=160, height=90, spp=2, bounces=3,
+        texture_extra={"clipping": "checker", "checker_dist": 0.2, "even_tiles": True, "odd_tiles": False, "interpolate": "none"},
+        mapper_extra={"texco": "global", "mapping": "cube", "scale": (0.7, 0.6, 0.5), "proj_x": 2, "proj_y": 3, "proj_z": 1},
+        layer_extra={"stencil": True, "negative": True, "upper_color": (0.5, 0.6, 0.7, 0.6)}),
+    "tex_orco_clip_crop_rot_screen_norgb": dict(scene="test01", width=160, height=90, spp=2, bounces=3, filter_type="box",
+        texture_extra={"clipping": "clip", "rot90": True, "cropmin_x": 0.1, "cropmax_y": 0.8},
+        mapper_extra={"scale": (1.7, 2.3, 1.0), "offset": (0.2, -0.3, 0.0)},
+        layer_extra={"blend_mode": "screen", "noRGB": True, "def_col": (0.9, 0.2, 0.1, 1.0)}),
+}
+
+
+def make_extra(configs, filename, cwd=None):
     from libyafaray_b200 import scenes_pt
 
     out = {}
     for key, kw in configs.items():
         rec = helpers.ScriptRecorder()
         scenes_pt.build(rec, **kw)
-        out[key] = helpers.ref_render(rec)[0]
+        out[key] = helpers.ref_render(rec, cwd=cwd)[0]
     np.savez_compressed(os.path.join(HERE, filename), **out)
+
+
+def make_test01():
+    import shutil
+
+    os.makedirs(TEST01_DIR, exist_ok=True)
+    for f in ("tex.tga", "tex.hdr"):
+        shutil.copyfile(os.path.join("/root/reference/tests/test01", f), os.path.join(TEST01_DIR, f))
+        os.chmod(os.path.join(TEST01_DIR, f), 0o644)
+    make_extra(PT_GOLDEN_TEST01, "pt_test01.npz", cwd=TEST01_DIR)
 
 
 def make_city():
     make_extra(PT_GOLDEN_CITY, "pt_city.npz")
     make_extra(PT_GOLDEN_DOF, "pt_dof.npz")
     make_extra(PT_GOLDEN_LIGHTS, "pt_lights.npz")
+    make_test01()
 
 
 def main():

@@ -127,6 +127,11 @@ def emu_pt_render(a, n_samples=None, offset=0, aa_pass=0, shard_index=0, shard_c
     w = np.zeros((pr.height, pr.width), np.float32) if film is None else film[0]
     rgba = np.zeros((pr.height, pr.width, 4), np.float32) if film is None else film[1]
     pl = None if pixel_list is None else np.ascontiguousarray(pixel_list, np.uint32)
+    st = emu().emu_pt_set_textures
+    st.restype = C.c_int
+    optr = a["tri_orco"].ctypes.data_as(C.c_void_p) if a.get("tri_orco") is not None else None
+    uptr = a["tri_uv"].ctypes.data_as(C.c_void_p) if a.get("tri_uv") is not None else None
+    assert st(a["textures"], C.c_uint32(a["n_tex"]), a["layers"], C.c_uint32(a["n_layers"]), optr, uptr, C.c_uint64(len(a["tris"]))) == 0
     f = emu().emu_pt_render
     f.restype = C.c_int
     nptr = a["normals"].ctypes.data_as(C.c_void_p) if a["normals"] is not None else None

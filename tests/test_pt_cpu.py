@@ -14,16 +14,18 @@ from libyafaray_b200._lib import Y4Error
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 sys.path.insert(0, GOLD)
-from make_golden import PT_GOLDEN, PT_GOLDEN_CITY, PT_GOLDEN_DOF, PT_GOLDEN_LIGHTS  # noqa: E402
+from make_golden import PT_GOLDEN, PT_GOLDEN_CITY, PT_GOLDEN_DOF, PT_GOLDEN_LIGHTS, PT_GOLDEN_TEST01, TEST01_DIR  # noqa: E402
 
 ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: ("pt_city.npz", v) for k, v in PT_GOLDEN_CITY.items()},
-              **{k: ("pt_dof.npz", v) for k, v in PT_GOLDEN_DOF.items()}, **{k: ("pt_lights.npz", v) for k, v in PT_GOLDEN_LIGHTS.items()}}
+              **{k: ("pt_dof.npz", v) for k, v in PT_GOLDEN_DOF.items()}, **{k: ("pt_lights.npz", v) for k, v in PT_GOLDEN_LIGHTS.items()},
+              **{k: ("pt_test01.npz", v) for k, v in PT_GOLDEN_TEST01.items()}}
 
 PSNR_MIN = 50.0  # BASELINE.json: PSNR >= 50 dB vs the reference at equal spp with identical sample sequences
 
 
 def _assemble(**kw):
     yi = interface.Interface()
+    yi.image_dir = TEST01_DIR
     scenes_pt.build(yi, accelerator="yafaray-b200-bvh8", **kw)
     return yi.assemble()
 
@@ -141,6 +143,66 @@ def test_interface_rejects_unsupported_features():
     yi.paramsSetString("scene_accelerator", "yafaray-kdtree-original")
     with pytest.raises(Y4Error):
         yi.setupRender()
+
+
+def test_texture_features_outside_the_supported_set_are_rejected_or_dropped_like_the_reference():
+    yi = interface.Interface()
+    yi.image_dir = TEST01_DIR
+    yi.paramsSetString("filename", "tex.tga")
+    assert yi.createImage("img")
+    yi.paramsClearAll()
+    yi.paramsSetString("filename", "tex.png")           # no PNG loader in a default reference build: no image, no exception
+    assert not yi.createImage("png_img") and yi.warnings
+    for bad in (dict(type="clouds"), dict(type="image", image_name="img", interpolate="bicubic"), dict(type="image", image_name="img", adj_hue=30.0),
+                dict(type="image", image_name="img", normalmap=True)):
+        yi.paramsClearAll()
+        scenes_pt._set_params(yi, bad)
+        with pytest.raises(Y4Error):
+            yi.createTexture("t")
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="image", image_name="png_img"))
+    assert not yi.createTexture("dropped")              # ImageTexture::factory returns nullptr
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="image", image_name="img"))
+    assert yi.createTexture("tex")
+
+    def material(layer=None, mapper=None, **mat):
+        yi.paramsClearAll()
+        scenes_pt._set_params(yi, dict(type="shinydiffusemat", diffuse_shader="l0", **mat))
+        yi.paramsPushList()
+        scenes_pt._set_params(yi, {**dict(element="shader_node", type="layer", name="l0", input="m0"), **(layer or {})})
+        yi.paramsPushList()
+        scenes_pt._set_params(yi, {**dict(element="shader_node", type="texture_mapper", name="m0", texture="tex"), **(mapper or {})})
+        yi.paramsEndList()
+        return yi.createMaterial("m")
+
+    assert material() and len(yi.materials["m"]["_diffuse_chain"]) == 1
+    for kw in (dict(mapper=dict(mapping="sphere")), dict(mapper=dict(texco="window")), dict(layer=dict(color_input=False)),
+               dict(bump_shader="l0"), dict(mapper=dict(type="value"))):
+        with pytest.raises(Y4Error):
+            material(**kw)
+    assert material(mapper=dict(texture="dropped")) and yi.materials["m"]["_diffuse_chain"] is None      # nodes dropped, plain colour
+    assert material(layer=dict(input="nowhere")) and yi.materials["m"]["_diffuse_chain"] is None
+
+
+def test_image_decoders_tga_hdr_storage_rounding():
+    """TGA: sRGB -> linear with the FAST_MATH pow, then the 10/10/10/8-bit "optimized" storage; HDR: RGBE as float, no rounding."""
+    from libyafaray_b200 import images
+
+    tga = images.load_image(dict(filename="tex.tga", color_space="sRGB", image_optimization="optimized"), TEST01_DIR)
+    hdr = images.load_image(dict(filename="tex.hdr", color_space="sRGB", image_optimization="optimized"), TEST01_DIR)
+    assert tga.shape == (300, 300, 4) and hdr.shape == (300, 300, 4) and tga.dtype == np.float32
+    q = tga[..., :3] * np.float32(1023.0)
+    assert np.abs(q - np.round(q)).max() < 1e-3 and np.abs(tga[..., 3] * 255 - np.round(tga[..., 3] * 255)).max() < 1e-4
+    assert 0.0 <= tga.min() and tga.max() <= 1.0 and len(np.unique(tga[..., 3])) > 2          # the file has a soft alpha channel
+    assert (hdr[..., 3] == 1.0).all() and hdr[..., :3].max() > 0.5
+    # exact properties of the restated pow: sRGB 1.0 -> 1023/1023 after rounding; values below the knee are divided by 12.92
+    assert images.linear_from_srgb(np.float32([0.04]))[0] == np.float32(0.04) / np.float32(12.92)
+    assert abs(float(images.linear_from_srgb(np.float32([1.0]))[0]) - 1.0) < 2e-4
+    lin = images.to_linear(np.float32([[0.5, 0.25, 1.0, 0.3]]), "sRGB", 1.0)
+    assert lin[0, 3] == np.float32(0.3) and abs(float(lin[0, 0]) - 0.21404) < 2e-4                # alpha is not converted
+    with pytest.raises(images.ImageLoadError):
+        images.load_image(dict(filename="tex.exr"), TEST01_DIR)
 
 
 def test_interface_primitive_and_light_order():
