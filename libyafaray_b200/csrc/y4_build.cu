@@ -96,6 +96,21 @@ __global__ void __launch_bounds__(256) k_refit(int n, const uint32_t *__restrict
 	}
 }
 
+// 5a. SAH refinement: collect the maximal subtrees with <= max_leaves leaves, rebuild each with binned SAH (one thread per treelet)
+__global__ void __launch_bounds__(256) k_treelet_roots(int n, int max_leaves, const int *__restrict__ parent, const int *__restrict__ first,
+                                                       const int *__restrict__ last, int *list, uint32_t *count)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= n - 1) return;
+	if(y4_is_treelet_root(n, max_leaves, parent, first, last, i)) list[atomicAdd(count, 1u)] = i;
+}
+__global__ void __launch_bounds__(64) k_treelet_sah(Y4TreeletArgs t, const int *__restrict__ list, const uint32_t *__restrict__ count)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= *count) return;
+	y4_treelet_sah(t, list[i]);
+}
+
 // 5b. surface-area sum of the binary tree's internal nodes: the part of the SAH cost that depends on the key order
 // (the leaves are the same single triangles either way)
 __global__ void __launch_bounds__(256) k_area_sum(const Y4Box *__restrict__ box, int n_internal, double *sum)
@@ -215,6 +230,18 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 		if(n > 1) k_karras<<<(n - 1 + tpb - 1) / tpb, tpb, 0, st>>>(keys, n, left.p, right.p, parent.p, first.p, last.p);
 		k_refit<<<grid_n, tpb, 0, st>>>(n, sorted_prim, tb.p, box.p, parent.p, left.p, right.p, flags.p);
 		ctx->stats.kernel_launches += 4;
+		if(ctx->treelet_leaves >= 3 && n > 2)
+		{
+			// `flags` (the refit's arrival counters) is free again: it holds the treelet root list; counters[3] their number
+			Y4_CUDA(ctx, cudaMemsetAsync(counters.p + 3, 0, sizeof(uint32_t), st));
+			k_treelet_roots<<<(n - 1 + tpb - 1) / tpb, tpb, 0, st>>>(n, ctx->treelet_leaves, parent.p, first.p, last.p, flags.p, counters.p + 3);
+			Y4TreeletArgs ta;
+			ta.n = n; ta.left = left.p; ta.right = right.p; ta.first = first.p; ta.last = last.p; ta.box = box.p; ta.sorted_prim = const_cast<uint32_t *>(sorted_prim);
+			// at most (n - 1) / 2 roots can exist (each has >= 3 leaves); the kernel reads the real count from the device
+			const int max_roots = (n - 1) / 2 + 1;
+			k_treelet_sah<<<(max_roots + 63) / 64, 64, 0, st>>>(ta, flags.p, counters.p + 3);
+			ctx->stats.kernel_launches += 2;
+		}
 		built_sized = sized;
 		if(!choose) break;
 		if(round < 2)

@@ -146,3 +146,134 @@ Y4_HD void y4_karras_node(const uint64_t *keys, int n, int i, int *left, int *ri
 	range_first[i] = lo; range_last[i] = hi;
 	if(i == 0) parent[0] = -1;
 }
+
+// ---- SAH refinement of the LBVH: treelet rebuild ----------------------------------------------------------
+// The Karras tree splits every range at a Morton-prefix boundary (a spatial median), whatever the triangle
+// distribution inside.  Every maximal subtree with at most `max_leaves` leaves (a "treelet") is rebuilt top-down with
+// the binned surface-area heuristic (16 bins per axis, cost = A_left * N_left + A_right * N_right): the leaves of its
+// range are re-ordered in place and its internal nodes re-linked.  Any binary tree over a contiguous range of sorted
+// leaves fits the Karras index space -- the left child of a split after leaf g is internal node g (or leaf g), the
+// right child internal node g + 1 (or leaf g + 1) -- so the tree above the treelet root, the root's own index and its
+// box stay as they are and the collapse to BVH8 runs unchanged.  (The kd-tree the reference builds is a full SAH tree,
+// accelerator_kdtree.cc:136-410; this recovers the SAH decisions where most nodes are, in the lower levels.)
+// One thread per treelet, sequential code (also run by the unit-test emulation); treelets are disjoint, so the
+// result does not depend on scheduling.  `parent` links are not maintained: nothing after the refit reads them.
+#define Y4_SAH_BINS 16
+struct Y4TreeletArgs
+{
+	int n;
+	int *left, *right, *first, *last;   // [n-1]
+	Y4Box *box;                         // [2n-1]
+	uint32_t *sorted_prim;              // [n]
+};
+Y4_HD bool y4_is_treelet_root(int n, int max_leaves, const int *parent, const int *first, const int *last, int i)
+{
+	const int m = last[i] - first[i] + 1;
+	if(m < 3 || m > max_leaves) return false;
+	if(i == 0) return true;
+	const int p = parent[i];
+	return last[p] - first[p] + 1 > max_leaves;
+}
+Y4_HD float y4_box_centre(const Y4Box &b, int axis)
+{
+	return axis == 0 ? 0.5f * (b.lox + b.hix) : (axis == 1 ? 0.5f * (b.loy + b.hiy) : 0.5f * (b.loz + b.hiz));
+}
+Y4_HD int y4_sah_bin(float c, float lo, float scale)
+{
+	const int b = (int) ((c - lo) * scale);
+	return b < 0 ? 0 : (b > Y4_SAH_BINS - 1 ? Y4_SAH_BINS - 1 : b);
+}
+Y4_HD void y4_treelet_sah(const Y4TreeletArgs &t, int root)
+{
+	const int n = t.n;
+	Y4Box *leaf = t.box + (n - 1);                   // leaf k of the sorted order
+	int stack[3 * 24];
+	int sp = 0;
+	int a = t.first[root], b = t.last[root], self = root;
+	for(;;)
+	{
+		const int m = b - a + 1;
+		// range box and centroid bounds
+		Y4Box rb = y4_box_empty();
+		float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+		for(int k = a; k <= b; ++k)
+		{
+			const Y4Box lb = leaf[k];
+			rb = y4_box_union(rb, lb);
+			for(int ax = 0; ax < 3; ++ax) { const float c = y4_box_centre(lb, ax); clo[ax] = fminf(clo[ax], c); chi[ax] = fmaxf(chi[ax], c); }
+		}
+		int g = a + (m >> 1) - 1;                    // fall-back: middle of the current order
+		if(m > 2)
+		{
+			float scale[3];
+			for(int ax = 0; ax < 3; ++ax) { const float e = chi[ax] - clo[ax]; scale[ax] = e > 0.f ? (float) Y4_SAH_BINS / e : 0.f; }
+			Y4Box bins[3][Y4_SAH_BINS];
+			int cnt[3][Y4_SAH_BINS];
+			for(int ax = 0; ax < 3; ++ax)
+				for(int q = 0; q < Y4_SAH_BINS; ++q) { bins[ax][q] = y4_box_empty(); cnt[ax][q] = 0; }
+			for(int k = a; k <= b; ++k)
+			{
+				const Y4Box lb = leaf[k];
+				for(int ax = 0; ax < 3; ++ax)
+				{
+					if(scale[ax] == 0.f) continue;
+					const int q = y4_sah_bin(y4_box_centre(lb, ax), clo[ax], scale[ax]);
+					bins[ax][q] = y4_box_union(bins[ax][q], lb);
+					++cnt[ax][q];
+				}
+			}
+			float best = FLT_MAX; int best_ax = -1, best_q = -1, best_nl = 0;
+			for(int ax = 0; ax < 3; ++ax)
+			{
+				if(scale[ax] == 0.f) continue;
+				float right_cost[Y4_SAH_BINS];       // A_right * N_right of the split after bin q
+				Y4Box acc = y4_box_empty(); int c = 0;
+				for(int q = Y4_SAH_BINS - 1; q >= 1; --q)
+				{
+					if(cnt[ax][q]) { acc = y4_box_union(acc, bins[ax][q]); c += cnt[ax][q]; }
+					right_cost[q - 1] = c ? y4_box_half_area(acc) * (float) c : FLT_MAX;
+				}
+				acc = y4_box_empty(); c = 0;
+				for(int q = 0; q < Y4_SAH_BINS - 1; ++q)
+				{
+					if(cnt[ax][q]) { acc = y4_box_union(acc, bins[ax][q]); c += cnt[ax][q]; }
+					if(c == 0 || right_cost[q] == FLT_MAX) continue;
+					const float cost = y4_box_half_area(acc) * (float) c + right_cost[q];
+					if(cost < best) { best = cost; best_ax = ax; best_q = q; best_nl = c; }
+				}
+			}
+			if(best_ax >= 0)
+			{
+				// in-place partition: bins <= best_q to the front
+				int i = a, j = b;
+				while(i <= j)
+				{
+					if(y4_sah_bin(y4_box_centre(leaf[i], best_ax), clo[best_ax], scale[best_ax]) <= best_q) { ++i; continue; }
+					if(y4_sah_bin(y4_box_centre(leaf[j], best_ax), clo[best_ax], scale[best_ax]) > best_q) { --j; continue; }
+					const Y4Box tb = leaf[i]; leaf[i] = leaf[j]; leaf[j] = tb;
+					const uint32_t tp = t.sorted_prim[i]; t.sorted_prim[i] = t.sorted_prim[j]; t.sorted_prim[j] = tp;
+					++i; --j;
+				}
+				g = a + best_nl - 1;
+			}
+		}
+		const int lc = (g == a) ? (n - 1 + a) : g;
+		const int rc = (g + 1 == b) ? (n - 1 + b) : (g + 1);
+		t.left[self] = lc; t.right[self] = rc; t.first[self] = a; t.last[self] = b; t.box[self] = rb;
+		// continue with the smaller internal child, keep the other one for later
+		const bool li = g > a, ri = g + 1 < b;
+		if(li && ri)
+		{
+			const bool left_small = (g - a) <= (b - g - 1);
+			if(left_small) { stack[sp++] = g + 1; stack[sp++] = b; stack[sp++] = g + 1; b = g; self = g; }
+			else { stack[sp++] = a; stack[sp++] = g; stack[sp++] = g; a = g + 1; self = g + 1; }
+		}
+		else if(li) { b = g; self = g; }
+		else if(ri) { a = g + 1; self = g + 1; }
+		else
+		{
+			if(sp == 0) break;
+			self = stack[--sp]; b = stack[--sp]; a = stack[--sp];
+		}
+	}
+}

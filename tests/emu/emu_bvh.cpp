@@ -5,6 +5,7 @@
 #include "../../libyafaray_b200/csrc/y4_trace.cuh"
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -43,6 +44,19 @@ void emu_build(const float *verts, const uint32_t *flags, int n, int leaf_max, E
 			if(flag[cur]++ == 0) break;
 			box[cur] = y4_box_union(box[left[cur]], box[right[cur]]);
 			cur = parent[cur];
+		}
+	}
+	// SAH treelet refinement (k_treelet_roots + k_treelet_sah of y4_build.cu); EMU_TREELET overrides the default size
+	{
+		const char *e = getenv("EMU_TREELET");
+		const int max_leaves = e ? atoi(e) : 512;
+		if(max_leaves >= 3 && n > 2)
+		{
+			std::vector<int> roots;
+			for(int i = 0; i < n - 1; ++i) if(y4_is_treelet_root(n, max_leaves, parent.data(), first.data(), last.data(), i)) roots.push_back(i);
+			Y4TreeletArgs ta;
+			ta.n = n; ta.left = left.data(); ta.right = right.data(); ta.first = first.data(); ta.last = last.data(); ta.box = box.data(); ta.sorted_prim = sorted_prim.data();
+			for(int r : roots) y4_treelet_sah(ta, r);
 		}
 	}
 	Y4BinTree bt;
