@@ -104,12 +104,183 @@ __global__ void __launch_bounds__(256) k_treelet_roots(int n, int max_leaves, co
 	if(i >= n - 1) return;
 	if(y4_is_treelet_root(n, max_leaves, parent, first, last, i)) list[atomicAdd(count, 1u)] = i;
 }
-__global__ void __launch_bounds__(64) k_treelet_sah(Y4TreeletArgs t, const int *__restrict__ list, const uint32_t *__restrict__ count)
+// One warp per treelet (CTA = 1 warp, persistent over the root list).  The leaf boxes of the treelet sit in shared memory
+// (SoA) and stay where they are; the splits permute a 16-bit index array.  Per split: warp-reduced range box and centroid
+// bounds, 3 x 16 bins filled with shared-memory atomics on order-preserving float encodings, the 45 candidate planes
+// costed by the lanes, warp arg-min (lowest candidate on ties, like the sequential y4_treelet_sah), stable ballot
+// partition.  Same decisions as y4_treelet_sah (y4_bvh_build.cuh), which the unit-test emulation runs.
+__device__ __forceinline__ float dec_f_dev(uint32_t e) { return __uint_as_float((e & 0x80000000u) ? (e & 0x7fffffffu) : ~e); }
+__device__ __forceinline__ float warp_min(float v) { for(int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o)); return v; }
+__device__ __forceinline__ float warp_max(float v) { for(int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o)); return v; }
+constexpr int kBinWords = 7;     // lo xyz, hi xyz (encoded), count
+
+// Two passes: the first one splits the big ranges of every treelet and hands the sub-ranges with <= defer_limit leaves
+// (most of the splits, each with a fixed per-split cost) to `defer_list`; the second pass runs the same kernel over that
+// list, one warp per small range, with far more warps in flight.
+__global__ void __launch_bounds__(32) k_treelet_sah(Y4TreeletArgs t, const int *__restrict__ list, const uint32_t *__restrict__ count, int K,
+                                                    int defer_limit, int *defer_list, uint32_t *defer_count)
 {
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if(i >= *count) return;
-	y4_treelet_sah(t, list[i]);
+	extern __shared__ __align__(16) unsigned char smem[];
+	float *bx = reinterpret_cast<float *>(smem);                         // [6][K]
+	uint32_t *prim = reinterpret_cast<uint32_t *>(bx + 6 * K);           // [K]
+	uint32_t *bins = prim + K;                                           // [3][16][7]
+	int *stack = reinterpret_cast<int *>(bins + 3 * Y4_SAH_BINS * kBinWords);   // [3 * 16]
+	uint16_t *idx = reinterpret_cast<uint16_t *>(stack + 48);            // [K]
+	uint16_t *idx2 = idx + K;                                            // [K]
+	const int lane = threadIdx.x;
+	const int n = t.n;
+	Y4Box *leaf = t.box + (n - 1);
+	const uint32_t n_roots = *count;
+	for(uint32_t ti = blockIdx.x; ti < n_roots; ti += gridDim.x)
+	{
+		const int root = list[ti];
+		const int lo = t.first[root], M = t.last[root] - lo + 1;
+		__syncwarp();
+		for(int k = lane; k < M; k += 32)
+		{
+			const Y4Box b = leaf[lo + k];
+			bx[k] = b.lox; bx[K + k] = b.loy; bx[2 * K + k] = b.loz; bx[3 * K + k] = b.hix; bx[4 * K + k] = b.hiy; bx[5 * K + k] = b.hiz;
+			prim[k] = t.sorted_prim[lo + k];
+			idx[k] = (uint16_t) k;
+		}
+		__syncwarp();
+		int sp = 0, a = 0, b = M - 1, self = root;
+		for(;;)
+		{
+			const int m = b - a + 1;
+			float rl[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, rh[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+			float clo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, chi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+			for(int k = a + lane; k <= b; k += 32)
+			{
+				const int j = idx[k];
+#pragma unroll
+				for(int ax = 0; ax < 3; ++ax)
+				{
+					const float l = bx[ax * K + j], h = bx[(3 + ax) * K + j], c = 0.5f * (l + h);
+					rl[ax] = fminf(rl[ax], l); rh[ax] = fmaxf(rh[ax], h); clo[ax] = fminf(clo[ax], c); chi[ax] = fmaxf(chi[ax], c);
+				}
+			}
+#pragma unroll
+			for(int ax = 0; ax < 3; ++ax) { rl[ax] = warp_min(rl[ax]); rh[ax] = warp_max(rh[ax]); clo[ax] = warp_min(clo[ax]); chi[ax] = warp_max(chi[ax]); }
+			int g = a + (m >> 1) - 1;
+			if(m > 2)
+			{
+				float scale[3];
+#pragma unroll
+				for(int ax = 0; ax < 3; ++ax) { const float e = chi[ax] - clo[ax]; scale[ax] = e > 0.f ? (float) Y4_SAH_BINS / e : 0.f; }
+				for(int w = lane; w < 3 * Y4_SAH_BINS * kBinWords; w += 32) { const int f = w % kBinWords; bins[w] = f < 3 ? 0xffffffffu : 0u; }
+				__syncwarp();
+				for(int k = a + lane; k <= b; k += 32)
+				{
+					const int j = idx[k];
+#pragma unroll
+					for(int ax = 0; ax < 3; ++ax)
+					{
+						if(scale[ax] == 0.f) continue;
+						const int q = y4_sah_bin(0.5f * (bx[ax * K + j] + bx[(3 + ax) * K + j]), clo[ax], scale[ax]);
+						uint32_t *B = bins + (ax * Y4_SAH_BINS + q) * kBinWords;
+						atomicMin(B + 0, enc_f(bx[j])); atomicMin(B + 1, enc_f(bx[K + j])); atomicMin(B + 2, enc_f(bx[2 * K + j]));
+						atomicMax(B + 3, enc_f(bx[3 * K + j])); atomicMax(B + 4, enc_f(bx[4 * K + j])); atomicMax(B + 5, enc_f(bx[5 * K + j]));
+						atomicAdd(B + 6, 1u);
+					}
+				}
+				__syncwarp();
+				float best = FLT_MAX; int best_c = 0x7fffffff, best_nl = 0;
+				for(int c = lane; c < 3 * (Y4_SAH_BINS - 1); c += 32)
+				{
+					const int ax = c / (Y4_SAH_BINS - 1), q = c % (Y4_SAH_BINS - 1);
+					if(scale[ax] == 0.f) continue;
+					Y4Box L = y4_box_empty(), R = y4_box_empty(); int nl = 0, nr = 0;
+					for(int w = 0; w < Y4_SAH_BINS; ++w)
+					{
+						const uint32_t *B = bins + (ax * Y4_SAH_BINS + w) * kBinWords;
+						const int cw = (int) B[6];
+						if(!cw) continue;
+						Y4Box bb; bb.lox = dec_f_dev(B[0]); bb.loy = dec_f_dev(B[1]); bb.loz = dec_f_dev(B[2]); bb.hix = dec_f_dev(B[3]); bb.hiy = dec_f_dev(B[4]); bb.hiz = dec_f_dev(B[5]);
+						if(w <= q) { L = y4_box_union(L, bb); nl += cw; } else { R = y4_box_union(R, bb); nr += cw; }
+					}
+					if(!nl || !nr) continue;
+					const float cost = y4_box_half_area(L) * (float) nl + y4_box_half_area(R) * (float) nr;
+					if(cost < best) { best = cost; best_c = c; best_nl = nl; }      // c ascends within a lane
+				}
+				for(int o = 16; o > 0; o >>= 1)
+				{
+					const float oc = __shfl_xor_sync(0xffffffffu, best, o);
+					const int ocand = __shfl_xor_sync(0xffffffffu, best_c, o), onl = __shfl_xor_sync(0xffffffffu, best_nl, o);
+					if(oc < best || (oc == best && ocand < best_c)) { best = oc; best_c = ocand; best_nl = onl; }
+				}
+				if(best_c != 0x7fffffff)
+				{
+					const int ax = best_c / (Y4_SAH_BINS - 1), q = best_c % (Y4_SAH_BINS - 1);
+					int base_l = a, base_r = a + best_nl;
+					for(int k0 = a; k0 <= b; k0 += 32)
+					{
+						const int k = k0 + lane;
+						const bool valid = k <= b;
+						const int j = valid ? idx[k] : 0;
+						const bool fl = valid && y4_sah_bin(0.5f * (bx[ax * K + j] + bx[(3 + ax) * K + j]), clo[ax], scale[ax]) <= q;
+						const uint32_t ml = __ballot_sync(0xffffffffu, fl), mr = __ballot_sync(0xffffffffu, valid && !fl);
+						const uint32_t lt = (1u << lane) - 1u;
+						if(fl) idx2[base_l + __popc(ml & lt)] = (uint16_t) j;
+						else if(valid) idx2[base_r + __popc(mr & lt)] = (uint16_t) j;
+						base_l += __popc(ml); base_r += __popc(mr);
+					}
+					__syncwarp();
+					for(int k = a + lane; k <= b; k += 32) idx[k] = idx2[k];
+					__syncwarp();
+					g = a + best_nl - 1;
+				}
+			}
+			if(lane == 0)
+			{
+				t.left[self] = (g == a) ? (n - 1 + lo + a) : (lo + g);
+				t.right[self] = (g + 1 == b) ? (n - 1 + lo + b) : (lo + g + 1);
+				t.first[self] = lo + a; t.last[self] = lo + b;
+				Y4Box rb; rb.lox = rl[0]; rb.loy = rl[1]; rb.loz = rl[2]; rb.hix = rh[0]; rb.hiy = rh[1]; rb.hiz = rh[2];
+				t.box[self] = rb;
+			}
+			// smaller internal child first, the other one on the stack (depth <= log2 K); uniform across the warp
+			bool li = g > a, ri = g + 1 < b;
+			if(defer_list)
+			{
+				if(li && g - a + 1 >= 3 && g - a + 1 <= defer_limit)
+				{
+					if(lane == 0) { t.first[lo + g] = lo + a; t.last[lo + g] = lo + g; defer_list[atomicAdd(defer_count, 1u)] = lo + g; }
+					li = false;
+				}
+				if(ri && b - g >= 3 && b - g <= defer_limit)
+				{
+					if(lane == 0) { t.first[lo + g + 1] = lo + g + 1; t.last[lo + g + 1] = lo + b; defer_list[atomicAdd(defer_count, 1u)] = lo + g + 1; }
+					ri = false;
+				}
+			}
+			if(li && ri)
+			{
+				if((g - a) <= (b - g - 1)) { if(lane == 0) { stack[sp] = g + 1; stack[sp + 1] = b; stack[sp + 2] = lo + g + 1; } sp += 3; b = g; self = lo + g; }
+				else { if(lane == 0) { stack[sp] = a; stack[sp + 1] = g; stack[sp + 2] = lo + g; } sp += 3; a = g + 1; self = lo + g + 1; }
+			}
+			else if(li) { b = g; self = lo + g; }
+			else if(ri) { a = g + 1; self = lo + g + 1; }
+			else
+			{
+				if(sp == 0) break;
+				__syncwarp();
+				sp -= 3;
+				a = stack[sp]; b = stack[sp + 1]; self = stack[sp + 2];
+				__syncwarp();
+			}
+		}
+		__syncwarp();
+		for(int k = lane; k < M; k += 32)
+		{
+			const int j = idx[k];
+			Y4Box o; o.lox = bx[j]; o.loy = bx[K + j]; o.loz = bx[2 * K + j]; o.hix = bx[3 * K + j]; o.hiy = bx[4 * K + j]; o.hiz = bx[5 * K + j];
+			leaf[lo + k] = o;
+			t.sorted_prim[lo + k] = prim[j];
+		}
+	}
 }
+static size_t treelet_smem_bytes(int K) { return (size_t) K * (6 * 4 + 4 + 2 + 2) + (3 * Y4_SAH_BINS * kBinWords + 48) * 4; }
 
 // 5b. surface-area sum of the binary tree's internal nodes: the part of the SAH cost that depends on the key order
 // (the leaves are the same single triangles either way)
@@ -237,9 +408,25 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 			k_treelet_roots<<<(n - 1 + tpb - 1) / tpb, tpb, 0, st>>>(n, ctx->treelet_leaves, parent.p, first.p, last.p, flags.p, counters.p + 3);
 			Y4TreeletArgs ta;
 			ta.n = n; ta.left = left.p; ta.right = right.p; ta.first = first.p; ta.last = last.p; ta.box = box.p; ta.sorted_prim = const_cast<uint32_t *>(sorted_prim);
-			// at most (n - 1) / 2 roots can exist (each has >= 3 leaves); the kernel reads the real count from the device
-			const int max_roots = (n - 1) / 2 + 1;
-			k_treelet_sah<<<(max_roots + 63) / 64, 64, 0, st>>>(ta, flags.p, counters.p + 3);
+			// persistent grid of one-warp CTAs; the kernel reads the number of roots from the device
+			const int K = ctx->treelet_leaves < n ? ctx->treelet_leaves : n;
+			const size_t smem = treelet_smem_bytes(K);
+			Y4_CUDA(ctx, cudaFuncSetAttribute(k_treelet_sah, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+			const int per_sm = (int) ((size_t) 200 * 1024 / smem) < 16 ? (int) ((size_t) 200 * 1024 / smem) : 16;
+			const int want = (n + 2) / 3;                    // upper bound of the number of roots (each has >= 3 leaves)
+			const int grid = want < ctx->sm_count * (per_sm > 0 ? per_sm : 1) ? want : ctx->sm_count * (per_sm > 0 ? per_sm : 1);
+			const int defer_limit = ctx->treelet_defer;
+			const bool two_pass = defer_limit >= 3 && K > defer_limit;
+			int *defer_list = flags.p + n / 2;                // second half of the buffer: at most n / 3 deferred ranges
+			Y4_CUDA(ctx, cudaMemsetAsync(counters.p + 2, 0, sizeof(uint32_t), st));
+			k_treelet_sah<<<grid, 32, smem, st>>>(ta, flags.p, counters.p + 3, K, defer_limit, two_pass ? defer_list : nullptr, counters.p + 2);
+			if(two_pass)
+			{
+				const size_t smem2 = treelet_smem_bytes(defer_limit);
+				const int grid2 = want < ctx->sm_count * 16 ? want : ctx->sm_count * 16;
+				k_treelet_sah<<<grid2, 32, smem2, st>>>(ta, defer_list, counters.p + 2, defer_limit, 0, nullptr, nullptr);
+				ctx->stats.kernel_launches++;
+			}
 			ctx->stats.kernel_launches += 2;
 		}
 		built_sized = sized;

@@ -45,7 +45,8 @@ struct y4gpu_ctx
 	int fetch_threshold = 20, postpone_div = 5, min_blocks = 3;
 	int morton_sized = -1;     // key order: -1 build both binary trees, keep the smaller surface-area sum; 0 plain 21-bit-per-axis Morton keys; 1 extended keys with size bits (env Y4GPU_MORTON_SIZED)
 	int morton_used = 0;       // what the last build chose
-	int treelet_leaves = 512;  // SAH rebuild of the binary subtrees with at most this many leaves (0 = plain LBVH; env Y4GPU_TREELET, <= 512)
+	int treelet_defer = 64;    // sub-ranges of a treelet with at most this many leaves are split by a second, wider launch (env Y4GPU_TREELET_DEFER; 0 = one pass)
+	int treelet_leaves = 2048;  // SAH rebuild of the binary subtrees with at most this many leaves (0 = plain LBVH; env Y4GPU_TREELET, <= 4096)
 
 	y4gpu_stats stats = {};
 	Y4Pt *pt = nullptr;

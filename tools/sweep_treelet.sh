@@ -1,4 +1,5 @@
-for K in 0 64 256 512; do
+# Sweep of the SAH-treelet size (Y4GPU_TREELET = leaves per rebuilt subtree, 0 = plain LBVH) on C3 rays, a 2 M-triangle C4 city and the Cornell headline.
+for K in ${KS:-0 512 2048 4096}; do
   echo "=== TREELET $K raybench" 
   Y4GPU_TREELET=$K timeout 300 python tools/raybench.py 1000 4096
   echo "=== TREELET $K c4 (2M tris 1080p)"
