@@ -247,7 +247,7 @@ Y4_HD void y4_light_sample_numbers(const Y4PtScene &sc, const Y4PtWave &W, const
 Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, bool all_lights, int light, int k, const Y4Vertex &vx, float4 cache)
 {
 	const uint32_t n = W.n;
-	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1);
+	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1 | Y4_PF_C1);
 	int l, num_samples;
 	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return 0u;
 	const Y4PtLight &L = sc.lights[l];
@@ -259,8 +259,11 @@ Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 	uint32_t mask = 0u;
 	for(int q = 0; q < 2; ++q)
 	{
-		st3(W.scontrib, q * n + i, out.contrib[q]);           // zero when the sample is invalid
-		if(!out.valid[q] || !cast) continue;
+		// zero when the sample is invalid; slot 1 (a BSDF-sampled direction that happens to reach the light) mostly is, and then
+		// neither it nor its read-back in the resolve step costs memory traffic
+		if(q == 0) st3(W.scontrib, i, out.contrib[0]);
+		else if(!cblack(out.contrib[1])) { st3(W.scontrib, n + i, out.contrib[1]); f |= Y4_PF_C1; }
+		if(!out.valid[q] || !cast || cblack(out.contrib[q])) continue;      // nothing to occlude: no shadow ray
 		st_ray(W.sray, q * n + i, out.ray[q]);
 		mask |= 1u << q;
 	}
@@ -277,18 +280,19 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 	int l, num_samples;
 	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return;
 	// everything this step can need, requested together
-	const float4 c0 = ld4(W.scontrib, i), c1 = ld4(W.scontrib, n + i);
+	const float4 zero4 = f4(0.f, 0.f, 0.f, 0.f);
+	const float4 c0 = ld4(W.scontrib, i), c1 = (f & Y4_PF_C1) ? ld4(W.scontrib, n + i) : zero4;
 	const int32_t p0 = (f & Y4_PF_S0) ? W.shit[i].prim : -1, p1 = (f & Y4_PF_S1) ? W.shit[n + i].prim : -1;
 	const float4 base = all_lights ? ld4(W.col, i) : ld4(W.pcol, i);
-	const float4 thr4 = all_lights ? f4(0.f, 0.f, 0.f, 0.f) : ld4(W.pthr, i);
-	const float4 lc4 = all_lights ? f4(0.f, 0.f, 0.f, 0.f) : ld4(W.lcol, i);
+	const float4 thr4 = all_lights ? zero4 : ld4(W.pthr, i);
+	const float4 lc4 = (all_lights || !(f & Y4_PF_LCOL)) ? zero4 : ld4(W.lcol, i);
 	const Y4PtLight &L = sc.lights[l];
 	// running sums over the light's samples live in acc_a/acc_b only between samples (k > 0)
 	C3 a = c3f(0.f), b = c3f(0.f);
 	if(k > 0) { a = ld3(W.acc_a, i); b = ld3(W.acc_b, i); }
 	if(p0 < 0) a = cadd(a, c3(c0.x, c0.y, c0.z));
 	if(p1 < 0) b = cadd(b, c3(c1.x, c1.y, c1.z));
-	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1);
+	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1 | Y4_PF_C1);
 	if(k < num_samples - 1) { st3(W.acc_a, i, a); st3(W.acc_b, i, b); return; }
 	// last sample of this light: doLightEstimation's result
 	C3 dl = c3f(0.f);
@@ -489,7 +493,7 @@ Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtP
 	if(what == 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return 0u; }
 	if(what == 2)
 	{
-		st3(W.lcol, i, emit);
+		if(!cblack(emit)) { st3(W.lcol, i, emit); f |= Y4_PF_LCOL; } else f &= ~(uint32_t) Y4_PF_LCOL;
 		st3(W.pthr, i, thr);
 		f |= Y4_PF_DIRECT;
 		push |= y4_pt_direct(sc, W, ps, i, f, false, -1, 0, vx, cache);

@@ -135,5 +135,7 @@ enum : uint32_t
 	Y4_PF_PATHS = 4u,            // primary material matches path_flags -> bounce loop runs
 	Y4_PF_DIFF1 = 8u,            // first path vertex's material has Diffuse (mat_bsd_fs, integrator_path_tracer.cc:196)
 	Y4_PF_DIRECT = 16u,          // the current vertex wants a one-light estimate this depth
-	Y4_PF_S0 = 32u, Y4_PF_S1 = 64u   // shadow-ray slot 0/1 of the current light sample was traced
+	Y4_PF_S0 = 32u, Y4_PF_S1 = 64u,  // shadow-ray slot 0/1 of the current light sample was traced
+	Y4_PF_C1 = 128u,             // W.scontrib slot 1 (the BSDF-sampled MIS estimator) holds a non-zero contribution; unset: it is zero and was not stored
+	Y4_PF_LCOL = 256u            // W.lcol holds non-zero emission picked up at the current vertex; unset: zero, not stored
 };
