@@ -221,6 +221,37 @@ def _load_hdr(data: bytes):
 LOADERS = {"tga": _load_tga, "tpic": _load_tga, "hdr": _load_hdr, "pic": _load_hdr}
 
 
+def empty_image(params: dict) -> np.ndarray:
+    """Image::factory for an image without a file (image.cc:38-60,103-140): width x height texels of the cleared buffer."""
+    t = str(params.get("type", "ColorAlpha"))
+    if t not in ("ColorAlpha", "Color"):
+        raise ImageLoadError(f"in-memory image type '{t}' is not supported by the GPU back end (ColorAlpha / Color)")
+    w, h = int(params.get("width", 100)), int(params.get("height", 100))
+    img = np.zeros((h, w, 4), f32)
+    if t == "Color":
+        img[..., 3] = 1.0
+    elif _optimization(params) == "none":
+        img[..., 3] = 0.0        # RgbAlpha buffers start as Rgba{0.f}; the optimised ones as all-zero bits (alpha 0 as well)
+    return img
+
+
+def _optimization(params: dict) -> str:
+    o = str(params.get("image_optimization", "optimized"))
+    return o if o in ("none", "optimized", "compressed") else "optimized"
+
+
+def storage_of(params: dict, texels: np.ndarray) -> tuple:
+    """(has alpha channel, optimisation) of the buffer createImage made: what setImageColor rounds through.
+    `params` is the dict load_image saw (it records the file's alpha rule under "_has_alpha")."""
+    fname = str(params.get("filename", ""))
+    ext = os.path.splitext(fname)[1].lower().lstrip(".")
+    if ext in ("hdr", "pic"):
+        return True, "none"
+    if fname:
+        return bool(params.get("_has_alpha", True)), _optimization(params)
+    return str(params.get("type", "ColorAlpha")) == "ColorAlpha", _optimization(params)
+
+
 def load_image(params: dict, search_dir: str = ".") -> np.ndarray:
     """Image::factory(params) for an image with a `filename` -> [height, width, 4] float32 texels (row y, column x)."""
     filename = str(params.get("filename", ""))
@@ -242,4 +273,5 @@ def load_image(params: dict, search_dir: str = ".") -> np.ndarray:
     raw, has_alpha = LOADERS[ext](data)
     if ext in ("hdr", "pic"):
         color_space, optimization = "LinearRGB", "none"
+    params["_has_alpha"] = has_alpha          # for setImageColor on a loaded image (storage_of)
     return np.ascontiguousarray(store(to_linear(raw, color_space, gamma), has_alpha, optimization), f32)

@@ -52,6 +52,7 @@ class Interface:
         self.eparams: List[Dict[str, object]] = []     # the ParamMap list of paramsPushList (shader nodes)
         self._cparams = self.params
         self.images: Dict[str, np.ndarray] = {}        # createImage: decoded texels [h, w, 4]
+        self._image_storage: Dict[str, tuple] = {}     # (has alpha channel, optimisation) of each image buffer
         self.textures: Dict[str, dict] = {}
         self.image_dir = "."                           # relative image file names resolve against this directory
         self.warnings: List[str] = []
@@ -107,12 +108,32 @@ class Interface:
     def createImage(self, name):
         """Scene::createImage -> Image::factory (image.cc:38-101).  A file the reference build cannot load leaves no
         image behind (False); textures and node materials that need it are then dropped like in the reference."""
+        p = dict(self.params)
         try:
-            self.images[name] = images.load_image(dict(self.params), self.image_dir)
+            if p.get("filename", ""):
+                self.images[name] = images.load_image(p, self.image_dir)
+            else:           # image in memory, filled with setImageColor (Image::factory(width, height, type, optimization), image.cc:103-140)
+                self.images[name] = images.empty_image(p)
         except images.ImageLoadError as exc:
             self.warnings.append(f"image '{name}': {exc}")
             return False
+        self._image_storage[name] = images.storage_of(p, self.images[name])
         return True
+
+    def setImageColor(self, name, x, y, r, g, b, a):
+        """yafaray_setImageColor -> Image::setColor(x, y, col): the colour goes through the image buffer's storage rounding."""
+        img = self.images.get(name)
+        if img is None or not (0 <= x < img.shape[1] and 0 <= y < img.shape[0]):
+            return False
+        has_alpha, optimization = self._image_storage[name]
+        img[y, x] = images.store(np.array([[r, g, b, a]], np.float32), has_alpha, optimization)[0]
+        return True
+
+    def getImageColor(self, name, x, y):
+        img = self.images.get(name)
+        if img is None or not (0 <= x < img.shape[1] and 0 <= y < img.shape[0]):
+            return None
+        return tuple(float(c) for c in img[y, x])
 
     def createTexture(self, name):
         """Scene::createTexture -> ImageTexture::factory (texture_image.cc:476-597)."""

@@ -542,6 +542,80 @@ def test01(api, width=480, height=270, spp=3, integrator="pathtracing", bounces=
     api.setupRender()
 
 
+# ---- the reference's tests/test00 scene: one cube, its texture filled pixel by pixel through the API -----------------
+def test00(api, width=400, height=400, spp=1, integrator="directlighting", bounces=3, tex=200, accelerator="yafaray-kdtree-original", threads=1,
+           filter_type="gauss"):
+    """tests/test00/test00.c of the reference (:107-232): an image is created from a TGA file without storage optimisation,
+    then every texel is overwritten with yafaray_setImageColor (HDR values up to 4); cube-mapped on orco coordinates.
+    The shipped file renders with photon mapping (or the commented-out `directlighting`); here direct lighting / path tracing."""
+    api.paramsClearAll()
+    api.paramsSetString("type", "ColorAlpha")
+    api.paramsSetString("image_optimization", "none")
+    api.paramsSetInt("tex_width", tex)
+    api.paramsSetInt("tex_height", tex)
+    api.paramsSetString("filename", "tex.tga")
+    api.createImage("Image01")
+    for i in range(tex):
+        for j in range(tex):
+            api.setImageColor("Image01", i, j, 0.01 * i, 0.01 * j, 0.01 * (i + j), 1.0)
+    api.paramsClearAll()
+    api.paramsSetString("type", "image")
+    api.paramsSetString("image_name", "Image01")
+    api.createTexture("TextureTGA")
+    api.paramsClearAll()
+    api.paramsSetString("type", "shinydiffusemat")
+    api.paramsSetColor("color", 0.9, 0.9, 0.9, 1.0)
+    api.paramsPushList()
+    _set_params(api, dict(element="shader_node", name="diff_layer0", input="map0", type="layer", blend_mode="mix", upper_color=(1.0, 1.0, 1.0, 1.0)))
+    api.paramsPushList()
+    _set_params(api, dict(element="shader_node", name="map0", type="texture_mapper", mapping="cube", texco="orco", texture="TextureTGA"))
+    api.paramsEndList()
+    api.paramsSetString("diffuse_shader", "diff_layer0")
+    api.createMaterial("MaterialTGA")
+
+    api.paramsClearAll()
+    api.paramsSetBool("has_orco", True)
+    api.paramsSetString("type", "mesh")
+    api.createObject("Cube")
+    for ix in (0, 1):
+        for iy in (0, 1):
+            for iz in (0, 1):
+                api.addVertexWithOrco((-4.0, -2.0)[ix], (1.5, 3.5)[iy], (0.0, 2.0)[iz], 2.0 * ix - 1.0, 2.0 * iy - 1.0, 2.0 * iz - 1.0)
+    api.setCurrentMaterial("MaterialTGA")
+    for t in TEST01_CUBE_TRIS:
+        api.addTriangle(*t)
+    api.endObject()
+
+    api.paramsClearAll()
+    _set_params(api, dict(type="pointlight", color=(1.0, 1.0, 1.0, 1.0), power=150.0))
+    api.paramsSetVector("from", 5.3, -4.9, 8.9)
+    api.createLight("light_1")
+    api.paramsClearAll()
+    _set_params(api, dict(type="constant", color=(1.0, 1.0, 1.0, 1.0)))
+    api.createBackground("world_background")
+    api.paramsClearAll()
+    _set_params(api, dict(type="perspective", resx=width, resy=height, focal=1.1))
+    api.paramsSetVector("from", 8.6, -7.2, 8.1)
+    api.paramsSetVector("to", 8.0, -6.7, 7.6)
+    api.paramsSetVector("up", 8.3, -6.8, 9.0)
+    api.createCamera("cam_1")
+    api.paramsClearAll()
+    api.paramsSetString("camera_name", "cam_1")
+    api.createRenderView("view_1")
+    api.paramsClearAll()
+    api.paramsSetString("type", integrator)
+    if integrator == "pathtracing":
+        _set_params(api, dict(bounces=bounces, path_samples=1, russian_roulette_min_bounces=bounces, caustic_type="none"))
+    api.createIntegrator("surfintegr")
+    api.paramsClearAll()
+    _set_params(api, dict(type="combined", image_type="ColorAlpha", exported_image_type="ColorAlpha", exported_image_name="Combined"))
+    api.defineLayer()
+    api.paramsClearAll()
+    _set_params(api, dict(integrator_name="surfintegr", background_name="world_background", scene_accelerator=accelerator, width=width, height=height,
+                          threads=threads, AA_passes=1, AA_minsamples=spp, AA_inc_samples=1, filter_type=filter_type, tiles_order="linear", tile_size=32))
+    api.setupRender()
+
+
 def build(api, scene="cornell", **kw):
     """Dispatch by scene name (the committed golden configurations carry a `scene` key)."""
-    return {"cornell": cornell_box, "city": city, "test01": test01}[scene](api, **kw)
+    return {"cornell": cornell_box, "city": city, "test01": test01, "test00": test00}[scene](api, **kw)

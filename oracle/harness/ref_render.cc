@@ -12,6 +12,7 @@
 //     defineLayer | startGeometry | endGeometry | endObject | setCurrentMaterial name
 //     addVertex x y z | addNormal x y z | addTriangle a b c | smoothMesh name angle
 //     addVertexWithOrco x y z ox oy oz | addUv u v | addTriangleWithUv a b c ua ub uc | createImage name | createTexture name
+//     setImageColor image_name x y r g b a
 //     loadMesh file   (binary: int32 n_vert, int32 n_tri, float32 verts[n_vert*3], int32 tris[n_tri*3] -> addVertex/addTriangle)
 //     addInstance base 16 floats | setupRender
 //     render out.f32  (renders; the Combined layer arrives through the put-pixel callback as float
@@ -22,6 +23,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <map>
 #include <sstream>
 #include <string>
 #include <vector>
@@ -62,6 +64,7 @@ int main(int argc, char **argv)
 	yafaray_setLogVerbosityLevel(yi, yafaray_logLevelFromString("mute"));
 	yafaray_createScene(yi);
 	Capture cap;
+	std::map<std::string, yafaray_Image_t *> images;
 	std::string line;
 	int lineno = 0;
 	while(std::getline(in, line))
@@ -86,7 +89,13 @@ int main(int argc, char **argv)
 		else if(cmd == "createIntegrator") { ss >> a; yafaray_createIntegrator(yi, a.c_str()); }
 		else if(cmd == "createRenderView") { ss >> a; yafaray_createRenderView(yi, a.c_str()); }
 		else if(cmd == "createObject") { ss >> a; yafaray_createObject(yi, a.c_str()); }
-		else if(cmd == "createImage") { ss >> a; yafaray_createImage(yi, a.c_str()); }
+		else if(cmd == "createImage") { ss >> a; images[a] = yafaray_createImage(yi, a.c_str()); }
+		else if(cmd == "setImageColor")
+		{
+			int x, y; float r, g, bb, al;
+			ss >> a >> x >> y >> r >> g >> bb >> al;
+			if(images.count(a) && images[a]) yafaray_setImageColor(images[a], x, y, r, g, bb, al);
+		}
 		else if(cmd == "createTexture") { ss >> a; yafaray_createTexture(yi, a.c_str()); }
 		else if(cmd == "createOutput") { ss >> a; yafaray_createOutput(yi, a.c_str()); }
 		else if(cmd == "defineLayer") yafaray_defineLayer(yi);

@@ -67,6 +67,9 @@ TEST01_DIR = os.path.join(HERE, "test01")
 PT_GOLDEN_TEST01 = {
     "c1_test01_pathtracing": dict(scene="test01", width=480, height=270, spp=3, bounces=4),
     "c1_test01_as_shipped_directlighting": dict(scene="test01", width=480, height=270, spp=3, integrator="directlighting"),
+    # tests/test00: the texture is filled texel by texel through yafaray_setImageColor (HDR values), un-optimised storage
+    "test00_setimagecolor_directlighting": dict(scene="test00", width=200, height=200, spp=1, integrator="directlighting"),
+    "test00_setimagecolor_pathtracing": dict(scene="test00", width=160, height=160, spp=2, integrator="pathtracing", bounces=3, tex=64),
     "tex_uv_repeat_mirror_adjust_multiply": dict(scene="test01", width=160, height=90, spp=2, bounces=3, with_uv=True,
         texture_extra={"xrepeat": 3, "yrepeat": 2, "mirror_x": True, "mirror_y": True, "adj_intensity": 1.2, "adj_contrast": 0.8,
                        "adj_mult_factor_red": 0.7, "adj_clamp": True},
@@ -97,7 +100,7 @@ def make_test01():
     import shutil
 
     os.makedirs(TEST01_DIR, exist_ok=True)
-    for f in ("tex.tga", "tex.hdr"):
+    for f in ("tex.tga", "tex.hdr"):        # tests/test00/tex.tga is the same file as tests/test01/tex.tga
         shutil.copyfile(os.path.join("/root/reference/tests/test01", f), os.path.join(TEST01_DIR, f))
         os.chmod(os.path.join(TEST01_DIR, f), 0o644)
     make_extra(PT_GOLDEN_TEST01, "pt_test01.npz", cwd=TEST01_DIR)

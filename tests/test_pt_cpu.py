@@ -205,6 +205,26 @@ def test_image_decoders_tga_hdr_storage_rounding():
         images.load_image(dict(filename="tex.exr"), TEST01_DIR)
 
 
+def test_set_image_color_goes_through_the_image_buffer_storage():
+    """yafaray_setImageColor / getImageColor on in-memory and loaded images (Image::setColor rounding per optimisation mode)."""
+    yi = interface.Interface()
+    yi.image_dir = TEST01_DIR
+    scenes_pt._set_params(yi, dict(type="ColorAlpha", image_optimization="optimized", width=4, height=3))
+    assert yi.createImage("mem")
+    assert yi.getImageColor("mem", 3, 2) == (0.0, 0.0, 0.0, 0.0) and yi.getImageColor("mem", 4, 0) is None
+    assert yi.setImageColor("mem", 1, 2, 0.5, 0.25, 1.0, 0.3) and not yi.setImageColor("mem", 0, 3, 0, 0, 0, 0)
+    r, g, b, a = yi.getImageColor("mem", 1, 2)
+    assert r == np.float32(512.0) / np.float32(1023.0) and g == np.float32(256.0) / np.float32(1023.0) and b == 1.0
+    assert a == np.float32(77.0) / np.float32(255.0)                      # roundf(0.3 * 255) = 77 (8-bit alpha)
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="Color", image_optimization="none", width=2, height=2))
+    assert yi.createImage("rgb") and yi.setImageColor("rgb", 0, 0, 3.5, 0.1, 0.2, 0.4)
+    assert yi.getImageColor("rgb", 0, 0) == (3.5, float(np.float32(0.1)), float(np.float32(0.2)), 1.0)      # no alpha channel: reads back 1
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="Gray", width=2, height=2))
+    assert not yi.createImage("gray") and yi.warnings
+
+
 def test_interface_primitive_and_light_order():
     """Objects by name (std::map order, scene.cc:1034), faces in insertion order, invisible/base objects skipped."""
     yi = interface.Interface()
