@@ -276,7 +276,7 @@ typedef struct y4gpu_pt_aa_noise
 {
 	float threshold;              /* current AA threshold (the host adapts it between passes like TiledIntegrator::render) */
 	int32_t detect_color_noise;
-	int32_t dark_detection_type;  /* 0 none, 1 linear (the "curve" type is not supported) */
+	int32_t dark_detection_type;  /* 0 none, 1 linear, 2 curve (ImageFilm::darkThresholdCurveInterpolate) */
 	float dark_threshold_factor;
 	int32_t variance_edge_size, variance_pixels;
 	int32_t reserved[6];

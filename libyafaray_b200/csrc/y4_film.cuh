@@ -38,6 +38,18 @@ Y4_HD float y4_color_difference(const Y4Rgba &a, const Y4Rgba &b, bool use_rgb) 
 	return d;
 }
 
+// ImageFilm::darkThresholdCurveInterpolate (imagefilm.cc:799-815): piecewise-linear threshold over the pixel brightness
+Y4_HD float y4_dark_threshold_curve(float b)
+{
+	const float knot[14] = {0.10f, 0.20f, 0.30f, 0.40f, 0.50f, 0.60f, 0.70f, 0.80f, 0.90f, 1.00f, 1.20f, 1.40f, 1.80f, 0.f};
+	const float val[14] = {0.0001f, 0.0010f, 0.0020f, 0.0035f, 0.0055f, 0.0075f, 0.0100f, 0.0150f, 0.0250f, 0.0400f, 0.0800f, 0.0950f, 0.1000f, 0.f};
+	const float width[13] = {0.f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.10f, 0.20f, 0.20f, 0.40f};
+	if(b <= knot[0]) return val[0];
+	for(int k = 1; k < 13; ++k)
+		if(b <= knot[k]) return xadd(val[k - 1], xdiv(xmul(xsub(b, knot[k - 1]), xsub(val[k], val[k - 1])), width[k]));
+	return 0.1000f;
+}
+
 // phase 1 (imagefilm.cc:301-309): pixels that have no sample at all are always resampled
 Y4_HD void y4_film_flag_init(const float *weights, uint8_t *flags, size_t p) { flags[p] = weights[p] > 0.f ? 0 : 1; }
 
@@ -49,6 +61,7 @@ Y4_HD void y4_film_flag_detect(const float *weights, const float *rgba, int widt
 	float thr = aa.threshold;
 	if(aa.dark_detection_type == 1 && aa.dark_threshold_factor > 0.f)
 		thr = xmul(aa.threshold, xadd(xsub(1.f, aa.dark_threshold_factor), xmul(y4_abscol2bri(pix), aa.dark_threshold_factor)));
+	else if(aa.dark_detection_type == 2) thr = y4_dark_threshold_curve(y4_abscol2bri(pix));
 	const size_t p = (size_t) y * (size_t) width + (size_t) x;
 	if(y4_color_difference(pix, y4_film_pixel(weights, rgba, width, x + 1, y), rgbn) >= thr) { flags[p] = 1; flags[p + 1] = 1; }
 	if(y4_color_difference(pix, y4_film_pixel(weights, rgba, width, x, y + 1), rgbn) >= thr) { flags[p] = 1; flags[p + (size_t) width] = 1; }

@@ -466,7 +466,7 @@ int y4gpu_pt_next_pass(y4gpu_ctx *ctx, const y4gpu_pt_aa_noise *aa, const float 
 	std::lock_guard<std::mutex> lock(ctx->mtx);
 	Y4Pt *pt = ctx->pt;
 	if(!pt || !pt->scene_set) { ctx->err = "y4gpu_pt_next_pass before y4gpu_pt_set_scene"; return Y4GPU_ERR_ARG; }
-	if(aa->dark_detection_type != 0 && aa->dark_detection_type != 1) { ctx->err = "AA_dark_detection_type 'curve' is not supported by the GPU back end"; return Y4GPU_ERR_UNSUPPORTED; }
+	if(aa->dark_detection_type < 0 || aa->dark_detection_type > 2) { ctx->err = "unknown AA_dark_detection_type"; return Y4GPU_ERR_ARG; }
 	if(d_weights && (!pt_is_device_ptr(d_weights) || !pt_is_device_ptr(d_rgba))) { ctx->err = "film buffers must be device memory"; return Y4GPU_ERR_ARG; }
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	cudaStream_t st = ctx->stream;

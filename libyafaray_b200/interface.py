@@ -611,9 +611,7 @@ class Interface:
         aa.threshold = float(rp.get("AA_threshold", 0.05)) if threshold is None else float(threshold)
         aa.detect_color_noise = int(bool(rp.get("AA_detect_color_noise", False)))
         ddt = str(rp.get("AA_dark_detection_type", "none"))
-        if ddt == "curve":
-            raise Y4Error("AA_dark_detection_type 'curve' is not supported by the GPU back end")
-        aa.dark_detection_type = 1 if ddt == "linear" else 0
+        aa.dark_detection_type = {"linear": 1, "curve": 2}.get(ddt, 0)
         aa.dark_threshold_factor = float(rp.get("AA_dark_threshold_factor", 0.0))
         aa.variance_edge_size, aa.variance_pixels = int(rp.get("AA_variance_edge_size", 10)), int(rp.get("AA_variance_pixels", 0))
         return aa

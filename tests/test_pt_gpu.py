@@ -122,6 +122,7 @@ ADAPTIVE = [
     dict(AA_passes=3, AA_inc_samples=2, AA_threshold=0.03),
     dict(AA_passes=4, AA_inc_samples=1, AA_threshold=0.02, AA_resampled_floor=60.0, AA_detect_color_noise=True, AA_variance_pixels=4, AA_variance_edge_size=6,
          AA_dark_detection_type="linear", AA_dark_threshold_factor=0.5, AA_sample_multiplier_factor=1.5),
+    dict(AA_passes=4, AA_inc_samples=2, AA_threshold=0.02, AA_dark_detection_type="curve"),
 ]
 
 
