@@ -222,7 +222,10 @@ typedef struct y4gpu_pt_camera    /* `perspective` camera parameters (camera_per
 	float from[3], to[3], up[3];
 	int32_t resx, resy;
 	float aspect_ratio, focal, aperture, dof_distance, near_clip, far_clip;
-	int32_t reserved[4];
+	int32_t bokeh_type;           /* lens shape when aperture != 0: 0 disk1 (default), 1 disk2, 3 triangle, 4 square, 5 pentagon, 6 hexagon, 7 ring */
+	int32_t bokeh_bias;           /* 0 uniform, 1 center, 2 edge */
+	float bokeh_rotation;         /* degrees (polygonal lens shapes) */
+	int32_t reserved[1];
 } y4gpu_pt_camera;
 
 enum { Y4GPU_FILTER_BOX = 0, Y4GPU_FILTER_GAUSS = 1, Y4GPU_FILTER_MITCHELL = 2, Y4GPU_FILTER_LANCZOS = 3 };

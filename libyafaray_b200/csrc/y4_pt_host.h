@@ -47,6 +47,16 @@ inline Y4PtCamera derive_camera(const y4gpu_pt_camera &c)
 	o.resx = c.resx; o.resy = c.resy;
 	o.aperture = c.aperture; o.dof_distance = c.dof_distance;
 	o.dof_rt = tov(c.aperture * cam_x); o.dof_up = tov(c.aperture * cam_y);       // setAxis: "premul with aperture"
+	o.bkhtype = c.bokeh_type; o.bkhbias = c.bokeh_bias;
+	for(int i = 0; i < 16; ++i) o.ls[i] = 0.f;
+	int ns = c.bokeh_type;
+	if(ns >= 3 && ns <= 6)              // ctor: corner table of the polygonal lens, FAST_TRIG cos / sin, long double constants
+	{
+		float w = (float) ((long double) c.bokeh_rotation * 0.017453292519943295769236907684886L);      // math::degToRad
+		const float wi = (float) (6.283185307179586476925286766559L / (long double) (float) ns);
+		ns = (ns + 2) * 2;
+		for(int i = 0; i < ns; i += 2) { o.ls[i] = y4_fast_cos(w); o.ls[i + 1] = y4_fast_sin(w); w += wi; }
+	}
 	return o;
 }
 

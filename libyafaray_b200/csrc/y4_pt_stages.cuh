@@ -120,7 +120,39 @@ Y4_HD void y4_shirley_disk(float r_1, float r_2, float &u, float &v)
 	v = xmul(r, y4_fast_sin(phi));
 }
 
-// PerspectiveCamera::shootRay (camera_perspective.cc:128-146); lu, lv: lens sample (used when aperture != 0, disk bokeh)
+// PerspectiveCamera::biasDist / sampleTsd / getLensUv (camera_perspective.cc:71-126): lens sample -> lens coordinates
+Y4_HD float y4_bias_dist(int bias, float r)
+{
+	if(bias == 1) return xsqrt(xmul(xsqrt(r), r));
+	if(bias == 2) return xsqrt(xsub(1.f, xmul(r, r)));
+	return xsqrt(r);
+}
+Y4_HD void y4_lens_uv(const Y4PtCamera &cam, float r_1, float r_2, float &u, float &v)
+{
+	const int t = cam.bkhtype;
+	if(t >= 3 && t <= 6)
+	{
+		const float fn = (float) t;
+		int idx = (int) xmul(r_1, fn);
+		r_1 = xmul(xsub(r_1, xdiv((float) idx, fn)), fn);
+		r_1 = y4_bias_dist(cam.bkhbias, r_1);
+		const float b_1 = xmul(r_1, r_2), b_0 = xsub(r_1, b_1);
+		idx <<= 1;
+		u = xadd(xmul(cam.ls[idx], b_0), xmul(cam.ls[idx + 2], b_1));
+		v = xadd(xmul(cam.ls[idx + 1], b_0), xmul(cam.ls[idx + 3], b_1));
+	}
+	else if(t == 1 || t == 7)
+	{
+		const float w = xmul((float) Y4_2PI, r_2);
+		if(t == 7) r_1 = xsqrt(xadd(0.707106781f, 0.292893218f));
+		else r_1 = y4_bias_dist(cam.bkhbias, r_1);
+		u = xmul(r_1, y4_fast_cos(w));
+		v = xmul(r_1, y4_fast_sin(w));
+	}
+	else y4_shirley_disk(r_1, r_2, u, v);
+}
+
+// PerspectiveCamera::shootRay (camera_perspective.cc:128-146); lu, lv: lens sample (used when aperture != 0)
 Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py, float lu, float lv)
 {
 	V3 d = xadd3(xadd3(xscale(cam.vright, px), xscale(cam.vup, py)), cam.vto);
@@ -132,7 +164,7 @@ Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py, float lu, f
 	if(cam.aperture != 0.f)
 	{
 		float u, v;
-		y4_shirley_disk(lu, lv, u, v);
+		y4_lens_uv(cam, lu, lv, u, v);
 		const V3 li = xadd3(xscale(cam.dof_rt, u), xscale(cam.dof_up, v));
 		from = xadd3(from, li);
 		d = xnormalize(xsub3(xscale(d, cam.dof_distance), li));

@@ -229,8 +229,6 @@ class Interface:
         p = dict(self.params)
         if p.get("type") != "perspective":
             raise Y4Error(f"camera type '{p.get('type')}' is not supported by the GPU back end")
-        if float(p.get("aperture", 0.0)) != 0.0 and (p.get("bokeh_type", "disk1") != "disk1" or p.get("bokeh_bias", "uniform") != "uniform"):
-            raise Y4Error("depth of field is supported with the default lens only (bokeh_type=disk1, bokeh_bias=uniform)")
         self.cameras[name] = p
         return True
 
@@ -440,6 +438,10 @@ class Interface:
         cam.aspect_ratio, cam.focal = float(cam_p.get("aspect_ratio", 1.0)), float(cam_p.get("focal", 1.0))
         cam.aperture, cam.dof_distance = float(cam_p.get("aperture", 0.0)), float(cam_p.get("dof_distance", 0.0))
         cam.near_clip, cam.far_clip = float(cam_p.get("nearClip", 0.0)), float(cam_p.get("farClip", -1.0))
+        # unknown names select the defaults, like PerspectiveCamera::factory (camera_perspective.cc:207-218)
+        cam.bokeh_type = _lib.BOKEH_TYPES.get(str(cam_p.get("bokeh_type", "disk1")), 0)
+        cam.bokeh_bias = _lib.BOKEH_BIAS.get(str(cam_p.get("bokeh_bias", "uniform")), 0)
+        cam.bokeh_rotation = float(cam_p.get("bokeh_rotation", 0.0))
 
         # textures + layer chains of the diffuse_shader slots (only the textures some chain uses are uploaded)
         tex_index: Dict[str, int] = {}

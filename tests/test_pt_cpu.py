@@ -122,9 +122,7 @@ def test_interface_rejects_unsupported_features():
     with pytest.raises(Y4Error):
         yi.createMaterial("t")
     yi.paramsClearAll()
-    yi.paramsSetString("type", "perspective")
-    yi.paramsSetFloat("aperture", 0.1)
-    yi.paramsSetString("bokeh_type", "hexagon")
+    yi.paramsSetString("type", "orthographic")
     with pytest.raises(Y4Error):
         yi.createCamera("c")
     yi.paramsClearAll()
@@ -204,6 +202,24 @@ def test_image_decoders_tga_hdr_storage_rounding():
     assert lin[0, 3] == np.float32(0.3) and abs(float(lin[0, 0]) - 0.21404) < 2e-4                # alpha is not converted
     with pytest.raises(images.ImageLoadError):
         images.load_image(dict(filename="tex.exr"), TEST01_DIR)
+
+
+BOKEH = [dict(bokeh_type="hexagon", bokeh_rotation=20.0), dict(bokeh_type="triangle", bokeh_bias="center"), dict(bokeh_type="square", bokeh_bias="edge"),
+         dict(bokeh_type="pentagon", bokeh_rotation=-35.0), dict(bokeh_type="disk2", bokeh_bias="center"), dict(bokeh_type="disk2"), dict(bokeh_type="ring")]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("bokeh", BOKEH)
+def test_lens_shapes_vs_live_reference(bokeh):
+    """PerspectiveCamera::getLensUv: polygonal lenses (corner table from the rotation), disk2 / ring, the three bias rules."""
+    kw = dict(width=48, height=27, spp=4, bounces=2, aperture=0.08, dof_distance=1.9, bokeh=bokeh)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    w, rgba = helpers.emu_pt_render(_assemble(**kw))
+    img = interface.normalize_film(w, rgba)
+    assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max()))
 
 
 def test_set_image_color_goes_through_the_image_buffer_storage():
