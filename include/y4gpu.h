@@ -286,8 +286,8 @@ typedef struct y4gpu_pt_aa_noise
 } y4gpu_pt_aa_noise;
 
 /* Per-triangle material index travels in the flag word of y4gpu_upload_triangles (bits 8..31).
- * vertex_normals: n_tri*9 floats (exported normals: shading normal interpolated like
- * primitive_triangle.cc:104-114) or NULL for flat shading. */
+ * vertex_normals: n_tri*9 floats (exported or smoothed normals at the three corners: shading normal interpolated like
+ * primitive_triangle.cc:104-114; a NaN in a triangle's first float = flat-shaded triangle) or NULL for flat shading. */
 /* Textures, layer chains and the per-triangle texture coordinates they read; call after y4gpu_build and BEFORE
  * y4gpu_pt_set_scene (materials refer to layers by index).  tri_orco: n_tri*9 floats, the three orco points of every
  * triangle (yafaray_addVertexWithOrco), a NaN in the first float marks a triangle of a mesh without orco points

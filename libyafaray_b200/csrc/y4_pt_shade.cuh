@@ -36,9 +36,9 @@ Y4_HD Y4Surf y4_surface(const Y4PtScene &sc, const V3 ray_o, const V3 ray_d, flo
 	const float4 ts = sc.tri_shade[(uint32_t) prim];
 	s.ng = v3(ts.x, ts.y, ts.z);
 	s.mat = y4_f2u(ts.w);
-	if(sc.normals)
+	const float *nn = sc.normals ? sc.normals + 9ull * (uint32_t) prim : nullptr;
+	if(nn && nn[0] == nn[0])        // NaN: a flat-shaded mesh next to smooth ones
 	{
-		const float *nn = sc.normals + 9ull * (uint32_t) prim;
 		const float u = xsub(xsub(1.f, bu), bv);                      // barycentric_u_ = 1 - u - v (:66)
 		const V3 n0 = v3(nn[0], nn[1], nn[2]), n1 = v3(nn[3], nn[4], nn[5]), n2 = v3(nn[6], nn[7], nn[8]);
 		s.n = xnormalize(xadd3(xadd3(xscale(n0, u), xscale(n1, bu)), xscale(n2, bv)));

@@ -37,6 +37,7 @@ class _Mesh:
         self.orco: List[tuple] = []        # addVertexWithOrco (MeshObject::orco_points_)
         self.uvs: List[tuple] = []         # addUv (MeshObject::uv_values_)
         self.tri_uvs: List[tuple] = []     # uv indices per face (addTriangleWithUv), None for addTriangle
+        self.smooth_angle: Optional[float] = None      # smoothMesh
         self.visibility = params.get("visibility", "normal")
         self.is_base = bool(params.get("is_base_object", False))
         self.instance_of: Optional[str] = None
@@ -327,7 +328,13 @@ class Interface:
         return True
 
     def smoothMesh(self, name, angle):
-        raise Y4Error("smoothMesh is not supported by the GPU back end (export vertex normals with addNormal instead)")
+        """Scene::smoothNormals (scene.cc:909-931): vertex normals from the face normals, MeshObject::smoothNormals."""
+        mesh = self.objects.get(name) if name else self._cur
+        if mesh is None:
+            return False
+        if not (mesh.normals and len(mesh.normals) == len(mesh.verts)):      # exported normals win
+            mesh.smooth_angle = float(np.float32(angle))
+        return True
 
     def addInstance(self, base_object_name, *m):
         if base_object_name not in self.objects:
@@ -379,6 +386,8 @@ class Interface:
             nn = None
             if base.normals and len(base.normals) == len(base.verts):
                 nn = np.asarray(base.normals, np.float64).astype(np.float32)[idx].reshape(-1, 9)
+            elif base.smooth_angle is not None and base.smooth_angle > 0.1:
+                nn = smooth_normals(v, idx, base.smooth_angle)
             oc = uv = None
             if textured:
                 if base.orco and len(base.orco) == len(base.verts):      # MeshObject::hasOrco
@@ -410,8 +419,8 @@ class Interface:
             if nn is not None and not o.instance_of:
                 normals.append(nn)
                 any_normals = True
-            else:
-                normals.append(None)
+            else:           # flat-shaded mesh in a scene that has smooth ones: NaN marks "shading normal = face normal" (include/y4gpu.h)
+                normals.append(np.full((len(idx), 9), np.nan, np.float32))
             flags.append(f)
         if tris:
             T = np.ascontiguousarray(np.concatenate(tris), np.float32)
@@ -420,8 +429,6 @@ class Interface:
             T, F = np.zeros((0, 9), np.float32), np.zeros(0, np.uint32)
         N = None
         if any_normals:
-            if any(x is None for x in normals):
-                raise Y4Error("exported vertex normals on only a subset of the objects are not supported yet")
             N = np.ascontiguousarray(np.concatenate(normals), np.float32)
 
         rp = self.render_params
@@ -712,6 +719,100 @@ class Interface:
         if self.accelerator is not None:
             self.accelerator.close()
             self.accelerator = None
+
+
+def _normalized(v: np.ndarray) -> np.ndarray:
+    """Vec3::normalize on rows (vector.h:201-210): len = 1 / sqrt(x*x + y*y + z*z), v *= len; null vectors stay."""
+    f32 = np.float32
+    l2 = (v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1]) + v[:, 2] * v[:, 2]
+    inv = np.where(l2 != 0, f32(1.0) / np.sqrt(np.where(l2 != 0, l2, f32(1.0))), f32(1.0)).astype(f32)
+    return (v * inv[:, None]).astype(f32)
+
+
+def _cross(a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    return np.stack([a[:, 1] * b[:, 2] - a[:, 2] * b[:, 1], a[:, 2] * b[:, 0] - a[:, 0] * b[:, 2], a[:, 0] * b[:, 1] - a[:, 1] * b[:, 0]], -1).astype(np.float32)
+
+
+def _length(v: np.ndarray) -> np.ndarray:
+    return np.sqrt((v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1]) + v[:, 2] * v[:, 2]).astype(np.float32)
+
+
+def smooth_normals(v: np.ndarray, idx: np.ndarray, angle: float) -> np.ndarray:
+    """MeshObject::smoothNormals (src/geometry/object/object_mesh.cc:118-240) -> the shading normal at the three corners of
+    every face, [n_tri, 9] fp32.  Face normals are weighted by the corner's angle (asin of Vec3::sinFromVectors, vector.h:212-219);
+    angle >= 180: one normal per vertex; otherwise only faces within `angle` of each other are blended, a corner that blends
+    with nothing keeps the face normal, and nearly equal normals at one vertex (dot > 0.999) share the first one found.
+    fp32 throughout, sums in the reference's order."""
+    f32 = np.float32
+    v = np.ascontiguousarray(v, f32)
+    idx = np.asarray(idx, np.int64)
+    n_tri = len(idx)
+    p = v[idx]                                                       # [n_tri, 3 corners, 3]
+    ng = _normalized(_cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0]))   # Primitive::getGeometricNormal (primitive_triangle.cc:87-95)
+    sines = np.empty((n_tri, 3), f32)
+    for c in range(3):
+        e1, e2 = p[:, (c + 1) % 3] - p[:, c], p[:, (c + 2) % 3] - p[:, c]
+        div = (_length(e1) * _length(e2)) * f32(0.99999) + f32(0.00001)
+        arg = np.minimum((_length(_cross(e1, e2)) / div) * f32(0.99999), f32(1.0)).astype(f32)
+        sines[:, c] = np.arcsin(arg.astype(np.float64)).astype(f32)     # std::asin(float): rounded from a more precise evaluation
+    out = np.repeat(ng, 3, axis=0).reshape(n_tri, 3, 3).copy()        # corners that stay unsmoothed use the face normal
+    if angle >= 180:
+        acc = np.zeros((len(v), 3), f32)
+        contrib = (ng[:, None, :] * sines[:, :, None]).astype(f32)    # n * sine, faces in order, corners 0, 1, 2
+        for k in range(3):
+            np.add.at(acc[:, k], idx.reshape(-1), contrib[:, :, k].reshape(-1))      # unbuffered: sums in face order
+        return np.ascontiguousarray(_normalized(acc)[idx].reshape(n_tri, 9), f32)
+    thr = _fast_cos_deg(angle)
+    order = np.argsort(idx.reshape(-1), kind="stable")               # incident (face, corner) pairs per vertex, faces in order
+    flat_v = idx.reshape(-1)[order]
+    starts = np.searchsorted(flat_v, np.arange(len(v) + 1))
+    for pt in range(len(v)):
+        inc = order[starts[pt]:starts[pt + 1]]
+        if len(inc) == 0:
+            continue
+        faces, corners = inc // 3, inc % 3
+        N, S = ng[faces], sines[faces, corners]
+        found = []                                                  # normals already created at this vertex
+        for j in range(len(inc)):
+            dots = (N[:, 0] * N[j, 0] + N[:, 1] * N[j, 1]) + N[:, 2] * N[j, 2]
+            vn = (N[j] * S[j]).astype(f32)
+            smooth = False
+            for k in range(len(inc)):
+                if faces[k] == faces[j]:
+                    continue
+                if dots[k] > thr:
+                    smooth = True
+                    vn = (vn + N[k] * S[k]).astype(f32)
+            if not smooth:
+                continue
+            vn = _normalized(vn[None, :])[0]
+            for e in found:
+                if (vn[0] * e[0] + vn[1] * e[1]) + vn[2] * e[2] > f32(0.999):
+                    vn = e
+                    break
+            else:
+                found.append(vn)
+            out[faces[j], corners[j]] = vn
+    return np.ascontiguousarray(out.reshape(n_tri, 9), f32)
+
+
+def _fast_cos_deg(angle: float) -> np.float32:
+    """math::cos(math::degToRad(angle)) with the FAST_TRIG polynomial (math.h:218-250)."""
+    f32 = np.float32
+    x = f32(np.longdouble(f32(angle)) * np.longdouble("0.017453292519943295769236907684886"))
+    x = f32(x + f32(np.longdouble("1.5707963267948966192313216916398")))
+    two_pi = f32(np.longdouble("6.283185307179586476925286766559"))
+    if x > two_pi or x < -two_pi:
+        x = f32(x - f32(int(x * f32(np.longdouble("0.15915494309189533576888376337251")))) * two_pi)
+    pi = np.longdouble("3.1415926535897932384626433832795")
+    if np.longdouble(x) < -pi:
+        x = f32(x + two_pi)
+    elif np.longdouble(x) > pi:
+        x = f32(x - two_pi)
+    x = f32(f32(np.longdouble("1.2732395447351626861510701069801") * np.longdouble(x))
+            - f32(np.longdouble("0.40528473456935108577551785283891") * np.longdouble(x) * np.longdouble(abs(x))))
+    r = f32(f32(0.225) * f32(f32(x * abs(x)) - x) + x)
+    return f32(min(max(r, f32(-1.0)), f32(1.0)))
 
 
 def normalize_film(w: np.ndarray, rgba: np.ndarray) -> np.ndarray:

@@ -58,9 +58,30 @@ def _box(lo, hi, yaw_deg, centre):
     return c.astype(np.float32), tris
 
 
+def _uv_sphere(centre, radius, nu, nv):
+    """Latitude / longitude sphere with shared vertices (so that yafaray_smoothMesh has something to smooth)."""
+    verts = [(centre[0], centre[1] + radius, centre[2])]
+    for j in range(1, nv):
+        th = np.pi * j / nv
+        for i in range(nu):
+            ph = 2.0 * np.pi * i / nu
+            verts.append((centre[0] + radius * np.sin(th) * np.cos(ph), centre[1] + radius * np.cos(th), centre[2] + radius * np.sin(th) * np.sin(ph)))
+    verts.append((centre[0], centre[1] - radius, centre[2]))
+    tris = []
+    ring = lambda j, i: 1 + (j - 1) * nu + (i % nu)
+    for i in range(nu):
+        tris.append((0, ring(1, i + 1), ring(1, i)))
+        tris.append((len(verts) - 1, ring(nv - 1, i), ring(nv - 1, i + 1)))
+    for j in range(1, nv - 1):
+        for i in range(nu):
+            tris.append((ring(j, i), ring(j, i + 1), ring(j + 1, i + 1)))
+            tris.append((ring(j, i), ring(j + 1, i + 1), ring(j + 1, i)))
+    return np.asarray(verts, np.float32), tris
+
+
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
-                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None):
+                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
@@ -94,6 +115,10 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     if not point_light:
         v, t = _quad((lx0, ly, lz0), (lx1, ly, lz0), (lx1, ly, lz1), (lx0, ly, lz1))
         _mesh(api, "h_lamp", "emitter", v, t)
+    if smooth_sphere is not None:       # a sphere on the short box, shaded with yafaray_smoothMesh(angle)
+        v, t = _uv_sphere((0.33, 0.42, 0.35), 0.12, 12, 7)
+        _mesh(api, "i_sphere", "white", v, t)
+        api.smoothMesh("i_sphere", float(smooth_sphere))
     api.endGeometry()
 
     api.paramsClearAll()

@@ -46,6 +46,8 @@ PT_GOLDEN_DOF = {
     # the other lens shapes of PerspectiveCamera::getLensUv: polygon corner table + edge bias, ring
     "dof_hexagon_edge": dict(scene="cornell", width=64, height=36, spp=4, bounces=3, aperture=0.08, dof_distance=1.9,
                              bokeh=dict(bokeh_type="hexagon", bokeh_bias="edge", bokeh_rotation=20.0)),
+    # yafaray_smoothMesh (angle-limited vertex normals) on a sphere next to flat-shaded meshes
+    "smooth_sphere_60": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, smooth_sphere=60.0),
     "dof_ring": dict(scene="cornell", width=64, height=36, spp=4, bounces=3, aperture=0.08, dof_distance=1.9, bokeh=dict(bokeh_type="ring")),
     # DirectLightIntegrator on the same stages (no path loop), 3 samples per light, gauss filter
     "direct_light3": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, integrator="directlighting", light_samples=3, filter_type="gauss"),

@@ -222,6 +222,22 @@ def test_lens_shapes_vs_live_reference(bokeh):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max()))
 
 
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("angle", [180.0, 60.0, 25.0])
+def test_smooth_mesh_vs_live_reference(angle):
+    """yafaray_smoothMesh: MeshObject::smoothNormals (one normal per vertex at 180 degrees, angle-limited blending below) next to
+    flat-shaded meshes in the same scene."""
+    kw = dict(width=64, height=36, spp=3, bounces=3, smooth_sphere=angle)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    a = _assemble(**kw)
+    assert a["normals"] is not None and np.isnan(a["normals"][0, 0]) and not np.isnan(a["normals"][-1]).any()
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
+
+
 def test_set_image_color_goes_through_the_image_buffer_storage():
     """yafaray_setImageColor / getImageColor on in-memory and loaded images (Image::setColor rounding per optimisation mode)."""
     yi = interface.Interface()
