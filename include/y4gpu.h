@@ -217,7 +217,9 @@ typedef struct y4gpu_pt_light
 	float blend;                  /* spotlight `blend` (default 0.15) */
 } y4gpu_pt_light;
 
-typedef struct y4gpu_pt_camera    /* `perspective` camera parameters (camera_perspective.cc:182-220) */
+enum { Y4GPU_CAM_PERSPECTIVE = 0, Y4GPU_CAM_ARCHITECT = 1, Y4GPU_CAM_ORTHOGRAPHIC = 2, Y4GPU_CAM_EQUIRECTANGULAR = 3 };
+typedef struct y4gpu_pt_camera    /* camera parameters: `perspective` (camera_perspective.cc:182-220), `architect` (camera_architect.cc),
+                                     `orthographic` (camera_orthographic.cc: `scale` travels in `focal`), `equirectangular` */
 {
 	float from[3], to[3], up[3];
 	int32_t resx, resy;
@@ -225,7 +227,7 @@ typedef struct y4gpu_pt_camera    /* `perspective` camera parameters (camera_per
 	int32_t bokeh_type;           /* lens shape when aperture != 0: 0 disk1 (default), 1 disk2, 3 triangle, 4 square, 5 pentagon, 6 hexagon, 7 ring */
 	int32_t bokeh_bias;           /* 0 uniform, 1 center, 2 edge */
 	float bokeh_rotation;         /* degrees (polygonal lens shapes) */
-	int32_t reserved[1];
+	int32_t type;                 /* Y4GPU_CAM_* */
 } y4gpu_pt_camera;
 
 enum { Y4GPU_FILTER_BOX = 0, Y4GPU_FILTER_GAUSS = 1, Y4GPU_FILTER_MITCHELL = 2, Y4GPU_FILTER_LANCZOS = 3 };

@@ -70,7 +70,7 @@ class PtCamera(C.Structure):
     _fields_ = [("from_", C.c_float * 3), ("to", C.c_float * 3), ("up", C.c_float * 3), ("resx", C.c_int32), ("resy", C.c_int32),
                 ("aspect_ratio", C.c_float), ("focal", C.c_float), ("aperture", C.c_float), ("dof_distance", C.c_float),
                 ("near_clip", C.c_float), ("far_clip", C.c_float), ("bokeh_type", C.c_int32), ("bokeh_bias", C.c_int32),
-                ("bokeh_rotation", C.c_float), ("reserved", C.c_int32 * 1)]  # fmt: skip
+                ("bokeh_rotation", C.c_float), ("type", C.c_int32)]  # fmt: skip
 
 
 class PtParams(C.Structure):
@@ -101,6 +101,7 @@ class PtAaNoise(C.Structure):
 MAT_SHINYDIFFUSE, MAT_LIGHT = 0, 1
 LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT = 0, 1, 2, 3, 4, 5
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
+CAMERA_TYPES = {"perspective": 0, "architect": 1, "orthographic": 2, "equirectangular": 3}
 BOKEH_TYPES = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}
 BOKEH_BIAS = {"uniform": 0, "center": 1, "edge": 2}
 CLIP_MODES = {"extend": 0, "clip": 1, "clipcube": 2, "repeat": 3, "checker": 4}

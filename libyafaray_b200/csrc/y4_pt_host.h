@@ -39,10 +39,29 @@ inline Y4PtCamera derive_camera(const y4gpu_pt_camera &c)
 	const HV near_p = position + cam_z * c.near_clip, far_p = position + cam_z * c.far_clip;
 	HV vright = cam_x;
 	HV vup = aspect_ratio * cam_y;
-	const HV vto = (cam_z * c.focal) - 0.5f * (vup + vright);
-	vup = {vup.x / (float) c.resy, vup.y / (float) c.resy, vup.z / (float) c.resy};
-	vright = {vright.x / (float) c.resx, vright.y / (float) c.resx, vright.z / (float) c.resx};
-	o.pos = tov(position); o.vright = tov(vright); o.vup = tov(vup); o.vto = tov(vto);
+	HV vto = (cam_z * c.focal) - 0.5f * (vup + vright);
+	HV origin = position;
+	o.type = c.type;
+	if(c.type == Y4GPU_CAM_ARCHITECT)                   // ArchitectCamera::setAxis (camera_architect.cc:52-66): verticals stay vertical
+	{
+		vup = aspect_ratio * HV{0.f, 0.f, -1.f};
+		vto = (cam_z * c.focal) - 0.5f * (vup + vright);
+	}
+	if(c.type == Y4GPU_CAM_ORTHOGRAPHIC)                // OrthographicCamera::setAxis (camera_orthographic.cc:37-49), scale in c.focal
+	{
+		const float scale = c.focal;
+		vto = cam_z;
+		origin = position - (float) (0.5 * scale) * (vup + vright);
+		const float sy = scale / (float) c.resy, sx = scale / (float) c.resx;
+		vup = vup * sy; vright = vright * sx;
+	}
+	else if(c.type == Y4GPU_CAM_EQUIRECTANGULAR) { vup = cam_y; vto = cam_z; }     // EquirectangularCamera::setAxis
+	else
+	{
+		vup = {vup.x / (float) c.resy, vup.y / (float) c.resy, vup.z / (float) c.resy};
+		vright = {vright.x / (float) c.resx, vright.y / (float) c.resx, vright.z / (float) c.resx};
+	}
+	o.pos = tov(origin); o.vright = tov(vright); o.vup = tov(vup); o.vto = tov(vto);
 	o.near_p = tov(near_p); o.near_n = tov(cam_z); o.far_p = tov(far_p); o.far_n = tov(cam_z);
 	o.resx = c.resx; o.resy = c.resy;
 	o.aperture = c.aperture; o.dof_distance = c.dof_distance;

@@ -155,6 +155,22 @@ Y4_HD void y4_lens_uv(const Y4PtCamera &cam, float r_1, float r_2, float &u, flo
 // PerspectiveCamera::shootRay (camera_perspective.cc:128-146); lu, lv: lens sample (used when aperture != 0)
 Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py, float lu, float lv)
 {
+	if(cam.type == Y4GPU_CAM_ORTHOGRAPHIC || cam.type == Y4GPU_CAM_EQUIRECTANGULAR)
+	{
+		// OrthographicCamera::shootRay (camera_orthographic.cc:52-60) / EquirectangularCamera::shootRay (camera_equirectangular.cc:50-62)
+		V3 from = cam.pos, d = cam.vto;
+		if(cam.type == Y4GPU_CAM_ORTHOGRAPHIC) from = xadd3(xadd3(cam.pos, xscale(cam.vright, px)), xscale(cam.vup, py));
+		else
+		{
+			const float u = xsub(xdiv(xmul(2.f, px), (float) cam.resx), 1.f), v = xsub(xdiv(xmul(2.f, py), (float) cam.resy), 1.f);
+			const float phi = (float) xdmul(Y4_PI, (Y4_WIDE) u), theta = (float) xdmul(Y4_PI_2, (Y4_WIDE) v);   // long double constants
+			const V3 h = xadd3(xscale(cam.vto, y4_fast_cos(phi)), xscale(cam.vright, y4_fast_sin(phi)));
+			d = xadd3(xscale(h, y4_fast_cos(theta)), xscale(cam.vup, y4_fast_sin(theta)));
+		}
+		const float tmin = xdiv(xdot(cam.near_n, xsub3(cam.near_p, from)), xdot(d, cam.near_n));
+		const float tmax = xdiv(xdot(cam.far_n, xsub3(cam.far_p, from)), xdot(d, cam.far_n));
+		return y4_mk_ray(from, tmin, d, tmax);
+	}
 	V3 d = xadd3(xadd3(xscale(cam.vright, px), xscale(cam.vup, py)), cam.vto);
 	d = xnormalize(d);
 	// Plane::rayIntersection: n * (p - from) / (dir * n)

@@ -35,6 +35,7 @@ struct Y4PtCamera          // PerspectiveCamera state after ctor + setAxis (came
 	// depth of field (aperture != 0): lens offsets dof_rt * u + dof_up * v, focus at dof_distance (camera_perspective.cc:58-59,136-143)
 	V3 dof_rt, dof_up;
 	float aperture, dof_distance;
+	int type;                   // Y4GPU_CAM_*: perspective and architect share shootRay, they differ in vup / vto
 	int bkhtype, bkhbias;       // BokehType / BkhBiasType (camera_perspective.h:38-39)
 	float ls[16];               // polygon corner directions of the tri / square / penta / hexa lenses (ctor, :40-52)
 };

@@ -228,7 +228,7 @@ class Interface:
 
     def createCamera(self, name):
         p = dict(self.params)
-        if p.get("type") != "perspective":
+        if p.get("type") not in _lib.CAMERA_TYPES:      # `angular` draws its ray from libm atan2 / tan: not restated
             raise Y4Error(f"camera type '{p.get('type')}' is not supported by the GPU back end")
         self.cameras[name] = p
         return True
@@ -442,9 +442,15 @@ class Interface:
         cam.to[:] = cam_p.get("to", (0.0, 0.0, 0.0))
         cam.up[:] = cam_p.get("up", (0.0, 1.0, 1.0))
         cam.resx, cam.resy = int(cam_p.get("resx", 320)), int(cam_p.get("resy", 200))
+        cam.type = _lib.CAMERA_TYPES[cam_p.get("type", "perspective")]
         cam.aspect_ratio, cam.focal = float(cam_p.get("aspect_ratio", 1.0)), float(cam_p.get("focal", 1.0))
-        cam.aperture, cam.dof_distance = float(cam_p.get("aperture", 0.0)), float(cam_p.get("dof_distance", 0.0))
-        cam.near_clip, cam.far_clip = float(cam_p.get("nearClip", 0.0)), float(cam_p.get("farClip", -1.0))
+        if cam.type == _lib.CAMERA_TYPES["orthographic"]:
+            cam.focal = float(cam_p.get("scale", 1.0))
+        if cam.type in (_lib.CAMERA_TYPES["perspective"], _lib.CAMERA_TYPES["architect"]):
+            cam.aperture, cam.dof_distance = float(cam_p.get("aperture", 0.0)), float(cam_p.get("dof_distance", 0.0))
+        # the factories' own defaults (camera_equirectangular.cc:70: farClip -1e38)
+        cam.near_clip = float(cam_p.get("nearClip", 0.0))
+        cam.far_clip = float(cam_p.get("farClip", -1.0e38 if cam.type == _lib.CAMERA_TYPES["equirectangular"] else -1.0))
         # unknown names select the defaults, like PerspectiveCamera::factory (camera_perspective.cc:207-218)
         cam.bokeh_type = _lib.BOKEH_TYPES.get(str(cam_p.get("bokeh_type", "disk1")), 0)
         cam.bokeh_bias = _lib.BOKEH_BIAS.get(str(cam_p.get("bokeh_bias", "uniform")), 0)

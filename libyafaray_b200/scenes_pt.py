@@ -81,7 +81,7 @@ def _uv_sphere(centre, radius, nu, nv):
 
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
-                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None):
+                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
@@ -190,6 +190,7 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         api.paramsSetFloat("aperture", aperture)
         _set_params(api, bokeh)         # bokeh_type / bokeh_bias / bokeh_rotation
         api.paramsSetFloat("dof_distance", dof_distance)
+    _set_params(api, camera_extra)      # another camera type / its parameters
     api.createCamera("cam")
 
     api.paramsClearAll()

@@ -48,6 +48,12 @@ PT_GOLDEN_DOF = {
                              bokeh=dict(bokeh_type="hexagon", bokeh_bias="edge", bokeh_rotation=20.0)),
     # yafaray_smoothMesh (angle-limited vertex normals) on a sphere next to flat-shaded meshes
     "smooth_sphere_60": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, smooth_sphere=60.0),
+    # the other camera types: orthographic, architect (with a square lens), equirectangular from inside the box
+    "cam_orthographic": dict(scene="cornell", width=64, height=36, spp=3, bounces=2, camera_extra=dict(type="orthographic", scale=1.3)),
+    "cam_architect_dof": dict(scene="cornell", width=64, height=36, spp=3, bounces=2,
+                              camera_extra=dict(type="architect", aperture=0.05, dof_distance=1.8, bokeh_type="square")),
+    "cam_equirectangular": dict(scene="cornell", width=64, height=36, spp=3, bounces=2,
+                                camera_extra={"type": "equirectangular", "from": (0.5, 0.5, 0.3), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, 0.3)}),
     "dof_ring": dict(scene="cornell", width=64, height=36, spp=4, bounces=3, aperture=0.08, dof_distance=1.9, bokeh=dict(bokeh_type="ring")),
     # DirectLightIntegrator on the same stages (no path loop), 3 samples per light, gauss filter
     "direct_light3": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, integrator="directlighting", light_samples=3, filter_type="gauss"),

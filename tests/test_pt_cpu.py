@@ -122,7 +122,7 @@ def test_interface_rejects_unsupported_features():
     with pytest.raises(Y4Error):
         yi.createMaterial("t")
     yi.paramsClearAll()
-    yi.paramsSetString("type", "orthographic")
+    yi.paramsSetString("type", "angular")
     with pytest.raises(Y4Error):
         yi.createCamera("c")
     yi.paramsClearAll()
@@ -220,6 +220,23 @@ def test_lens_shapes_vs_live_reference(bokeh):
     img = interface.normalize_film(w, rgba)
     assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max()))
+
+
+CAMERAS = [dict(type="orthographic", scale=1.3), dict(type="architect", focal=1.1), dict(type="architect", aperture=0.05, dof_distance=1.8, bokeh_type="square"),
+           dict(type="equirectangular", **{"from": (0.5, 0.5, 0.3), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, 0.3)})]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("cam", CAMERAS)
+def test_camera_types_vs_live_reference(cam):
+    """OrthographicCamera / ArchitectCamera / EquirectangularCamera::shootRay next to the perspective camera."""
+    kw = dict(width=64, height=36, spp=3, bounces=2, camera_extra=cam)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    w, rgba = helpers.emu_pt_render(_assemble(**kw))
+    img = interface.normalize_film(w, rgba)
+    assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
 
 
 @pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
