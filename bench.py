@@ -494,12 +494,27 @@ SHADE_BYTES = {
     "primary_miss": 16 + 32 + 8 + 16 + 4, "primary_hit": 16 + 32 + 8 + 16 + 16 + 16 + 16 + 4 + 32 + 32 + 8,
     # per camera hit: queue entry, flags, pix/samp, hit0, shadow hits, scontrib x2, col read; col, thr, flags, next ray, queue entry written
     "start": 4 + 4 + 8 + 16 + 8 + 32 + 16 + 16 + 16 + 4 + 32 + 4,
-    # per path-stage entry: queue entry, flags, hit, ray, thr, pix/samp, lsamp + previous estimate (shadow hits, scontrib x2, lcol, pthr, pcol) read;
-    # flags, pthr, thr, lcol, scontrib x2, 1 shadow ray, next ray, pcol, 2 queue entries written
-    "path": (4 + 4 + 16 + 32 + 16 + 8 + 16) + (8 + 32 + 16 + 16 + 16) + (4 + 16 + 16 + 16 + 32 + 32 + 32 + 16 + 8),
+    # per path-stage entry: queue entry, flags, hit, ray, thr, pix/samp, lsamp + previous estimate (shadow hits, scontrib, pthr, pcol) read;
+    # flags, pthr, thr, scontrib, 1 shadow ray, next ray, pcol, 2 queue entries written.  The second contribution slot and
+    # lcol move only when non-zero (flag bits) and are not counted: this is the lower bound the stage can reach.
+    "path": (4 + 4 + 16 + 32 + 16 + 8 + 16) + (8 + 16 + 16 + 16) + (4 + 16 + 16 + 16 + 32 + 32 + 16 + 8),
     # per pixel-sample: col, pcol, flags, pix/samp read; 5 float atomics to the film (box filter: one pixel)
     "splat": 16 + 16 + 4 + 8 + 5 * 4 * 2,
 }
+
+
+def measured_traffic(class_name, args):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel class, from the committed ncu capture of one
+    pass of the same workload (tools/ncu_traffic.py -> profiles/pt_traffic.json); None when the workload differs."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "pt_traffic.json")
+    want = "cornell %dx%d spp%d bounces%d" % (args.pt_width, args.pt_height, args.pt_spp, args.pt_bounces)
+    try:
+        t = json.load(open(path))
+        if t.get("workload") != want:
+            return None, "profiles/pt_traffic.json is for '%s', this run is '%s'" % (t.get("workload"), want)
+        return t["classes"][class_name]["dram_bytes_per_launch"], "profiles/pt_traffic.json (%s)" % t.get("source")
+    except (OSError, KeyError, ValueError) as e:
+        return None, "no capture: %s" % e
 
 
 def pt_arm(args, env):
@@ -606,6 +621,7 @@ def pt_arm(args, env):
         5: n * SHADE_BYTES["splat"],
     }
     achieved = alg_bytes[dom] / (cms[dom] * 1e-3) * 1e-9 if cms[dom] > 0 else 0.0
+    traffic, traffic_src = measured_traffic(names[dom], args)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -616,7 +632,9 @@ def pt_arm(args, env):
         "gpu_launches": int(launches),
         "roofline": {
             "bound": "hbm", "kernel": "%s kernels of one pass" % names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "launch_ms": cms[dom] / max(1, prof["class_launches"][dom]),
+            "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": alg_bytes[dom] / max(1, prof["class_launches"][dom]),
+            "launch_ms": cms[dom] / max(1, prof["class_launches"][dom]),
             "class_ms_per_pass": dict(zip(names, cms)), "class_launches_per_pass": dict(zip(names, prof["class_launches"][:6])),
             "class_algorithmic_GB": {names[k]: alg_bytes[k] * 1e-9 for k in range(6)},
             "pass_ms_profiled": sum(cms),

@@ -163,3 +163,28 @@ def test_transparent_shadow_mode_and_dof_match_the_cpu_emulation():
     img = yi.render()
     w, rgba = helpers.emu_pt_render(yi._assembled)
     assert helpers.psnr(img, interface.normalize_film(w, rgba)) >= 100.0
+
+
+def test_full_size_c2_film_properties():
+    """BASELINE config C2 at its full film size (1920x1080, 8 bounces): size-independent properties of a pass.
+    Box filter (weight 1 per covered pixel, AA_pixelwidth 1.5 reaches the neighbours): every pixel's weight is a whole
+    number >= 1 and the weights sum to at least the sample count; two shards sum to the unsharded film; a second run
+    agrees up to the order of the float atomics."""
+    kw = dict(width=1920, height=1080, spp=2, bounces=8)
+    one = _gpu(**kw)
+    one.render()
+    w1, c1 = one.read_film()
+    assert w1.shape == (1080, 1920) and (w1 >= 1.0).all() and np.array_equal(w1, np.round(w1))
+    assert float(w1.astype(np.float64).sum()) >= 1920 * 1080 * 2
+    assert np.isfinite(c1).all() and c1.min() >= 0.0 and (c1[..., 3] <= w1 * (1 + 1e-5)).all()
+    one.render()
+    w2, c2 = one.read_film()
+    assert np.array_equal(w1, w2) and np.allclose(c1, c2, rtol=1e-5, atol=1e-6)
+    ws, cs = 0, 0
+    for k in range(2):
+        yi = _gpu(shard_index=k, shard_count=2, **kw)
+        yi.render()
+        w, c = yi.read_film()
+        ws, cs = ws + w, cs + c
+    assert np.array_equal(w1, ws) and np.allclose(c1, cs, rtol=1e-5, atol=1e-5)
+    assert one.last_stats["samples"] == 1920 * 1080 * 2 and one.last_stats["rays_closest"] > one.last_stats["samples"]
