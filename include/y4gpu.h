@@ -134,12 +134,15 @@ int y4gpu_synchronize(y4gpu_ctx *ctx);
  *                           (imagefilm.cc:590-617)
  * Scene features outside the supported set are rejected with Y4GPU_ERR_UNSUPPORTED.            */
 
-enum { Y4GPU_MAT_SHINYDIFFUSE = 0, Y4GPU_MAT_LIGHT = 1 };
+enum { Y4GPU_MAT_SHINYDIFFUSE = 0, Y4GPU_MAT_LIGHT = 1,
+       Y4GPU_MAT_MIRROR = 2 };   /* `mirror` (MirrorMaterial, src/material/material_glass.cc:435-461): `color` and `reflect`
+                                    (in diffuse_reflect); perfect specular reflection, followed by the ray-level loop of
+                                    MonteCarloIntegrator::recursiveRaytrace up to `raydepth` and sampled inside paths */
 typedef struct y4gpu_pt_material
 {
 	int32_t type;                 /* Y4GPU_MAT_* */
 	float color[3];               /* shinydiffusemat `color` / light_mat `color` */
-	float diffuse_reflect;        /* shinydiffusemat: `diffuse_reflect` (default 1) */
+	float diffuse_reflect;        /* shinydiffusemat: `diffuse_reflect` (default 1); mirror: `reflect` (default 1) */
 	float emit;                   /* shinydiffusemat: `emit`; light_mat: `power` */
 	int32_t oren_nayar;           /* diffuse_brdf == "oren_nayar" */
 	float sigma;                  /* oren-nayar sigma */
@@ -254,7 +257,11 @@ typedef struct y4gpu_pt_params
 	                                 tmin <= t < t_max; accelerator_kdtree.cc:911-1061).  Every supported material is opaque,
 	                                 so a blocker always shadows and the filter colour is exactly 1 */
 	int32_t shadow_depth;         /* integrator shadowDepth (unused while every supported material is opaque) */
-	int32_t reserved[4];
+	int32_t raydepth;             /* integrator `raydepth` (default 5): specular recursion levels (integrator_montecarlo.cc:916-964) */
+	int32_t trace_caustics;       /* caustic_type path / both: emission found after a specular bounce of a path counts
+	                                 (integrator_path_tracer.cc:227,256-264) */
+	int32_t transp_refracted_background;   /* bg_transp_refract (TiledIntegrator::background, integrator_tiled.cc:707-720) */
+	int32_t reserved[1];
 } y4gpu_pt_params;
 
 typedef struct y4gpu_pt_stats

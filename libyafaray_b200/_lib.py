@@ -82,7 +82,8 @@ class PtParams(C.Structure):
                 ("aa_pixelwidth", C.c_float), ("aa_clamp_samples", C.c_float), ("filter_type", C.c_int32),
                 ("shadow_bias_auto", C.c_int32), ("shadow_bias", C.c_float), ("min_raydist_auto", C.c_int32), ("min_raydist", C.c_float),
                 ("base_sampling_offset", C.c_uint32), ("rr_seed", C.c_uint32), ("wave_size", C.c_uint32), ("profile", C.c_int32),
-                ("transp_shadows", C.c_int32), ("shadow_depth", C.c_int32), ("reserved", C.c_int32 * 4)]  # fmt: skip
+                ("transp_shadows", C.c_int32), ("shadow_depth", C.c_int32), ("raydepth", C.c_int32), ("trace_caustics", C.c_int32),
+                ("transp_refracted_background", C.c_int32), ("reserved", C.c_int32 * 1)]  # fmt: skip
 
 
 class PtStats(C.Structure):
@@ -98,7 +99,7 @@ class PtAaNoise(C.Structure):
                 ("variance_edge_size", C.c_int32), ("variance_pixels", C.c_int32), ("reserved", C.c_int32 * 6)]  # fmt: skip
 
 
-MAT_SHINYDIFFUSE, MAT_LIGHT = 0, 1
+MAT_SHINYDIFFUSE, MAT_LIGHT, MAT_MIRROR = 0, 1, 2
 LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT = 0, 1, 2, 3, 4, 5
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
 CAMERA_TYPES = {"perspective": 0, "architect": 1, "orthographic": 2, "equirectangular": 3}

@@ -46,7 +46,7 @@ struct Y4Pt
 	cudaEvent_t ev_fork = nullptr;
 	// per-launch counters: 64-bit slots, zeroed once per pass; a queue length is the low word of its slot
 	unsigned long long *d_counters = nullptr, *h_counters = nullptr; size_t counters_cap = 0;
-	std::vector<std::pair<uint32_t, int>> counter_kinds;      // (slot, kind) of the last pass: 0 traced path queue, 1 shadow queue, 2 camera-hit queue, 3 closing path queue
+	std::vector<std::pair<uint32_t, int>> counter_kinds;      // (slot, kind) of the last pass: 0 traced path queue, 1 shadow queue, 2 camera-hit queue, 3 closing path queue, 4 ray-level queue (mirror reflections)
 	uint64_t dense_closest = 0;
 	bool counters_read = true;
 	uint32_t *d_pixel_list = nullptr; uint64_t pixel_list_cap = 0;
@@ -78,12 +78,13 @@ namespace {
 constexpr int kPtThreads = 256;
 
 enum { kStPrimary, kStDirectStep, kStStart, kStPath };
-struct StageArgs { int all_lights, l_prev, k_prev, l, k, depth, sub; };
+struct StageArgs { int all_lights, l_prev, k_prev, l, k, depth, sub, level; };
 struct StageQueues
 {
 	const uint32_t *in_q, *in_count;     // null: dense over the wave
 	uint32_t *out_q, *out_count;         // paths that continue
 	uint32_t *sh_q, *sh_count;           // shadow rays to trace: slot index into W.sray / W.shit
+	uint32_t *spec_q, *spec_count;       // camera-hit stage only: pixel-samples whose ray a mirror reflected (next ray level)
 };
 
 __global__ void __launch_bounds__(kPtThreads) k_pt_gen(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, const uint32_t *__restrict__ pixel_list,
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 		if(q < count)
 		{
 			i = Q.in_q ? Q.in_q[q] : q;
-			if(STAGE == kStPrimary) push = y4_stage_primary(sc, W, ps, i, a.l);
+			if(STAGE == kStPrimary) push = y4_stage_primary(sc, W, ps, i, a.l, a.level);
 			else if(STAGE == kStDirectStep) push = y4_stage_direct_step(sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
 			else if(STAGE == kStStart) push = y4_stage_start(sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
 			else push = y4_stage_path(sc, W, ps, i, a.depth, a.sub, a.k_prev);
@@ -144,6 +145,17 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 			if(push & Y4_PUSH_S0) Q.sh_q[at_sh + __popc(m0 & lt_mask)] = i;
 			if(push & Y4_PUSH_S1) Q.sh_q[at_sh + __popc(m0) + __popc(m1 & lt_mask)] = W.n + i;
 			if(push & Y4_PUSH_PATH) Q.out_q[at_p + __popc(mp & lt_mask)] = i;
+		}
+		if(STAGE == kStPrimary && Q.spec_q)
+		{
+			const uint32_t ms = __ballot_sync(0xffffffffu, push & Y4_PUSH_SPEC);
+			if(ms)
+			{
+				uint32_t at = 0u;
+				if(lane == 0) at = atomicAdd(Q.spec_count, (uint32_t) __popc(ms));
+				at = __shfl_sync(0xffffffffu, at, 0);
+				if(push & Y4_PUSH_SPEC) Q.spec_q[at + __popc(ms & lt_mask)] = i;
+			}
 		}
 	}
 }
@@ -195,7 +207,7 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt::Lane &L, uint32_t cap)
 	if(cap <= L.cap) return Y4GPU_OK;
 	pt_free_wave(L);
 	const size_t n = cap;
-	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 16 /*pthr*/ + 2 * 32 + 16 + 16 /*ray x2 hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/
+	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 16 /*pthr*/ + 2 * 32 + 16 + 16 /*ray x2 hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/ + 32 + 16 /*ray0 sw*/
 	                          + 16 /*lsamp*/ + 5 * 4 /*queues*/) + 512;
 	Y4_CUDA(ctx, cudaMalloc(&L.mem, bytes));
 	char *p = (char *) L.mem;
@@ -205,6 +217,7 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt::Lane &L, uint32_t cap)
 	W.acc_a = (float *) take(n * 16); W.acc_b = (float *) take(n * 16); W.lsamp = (float *) take(n * 16);
 	W.ray = (Y4Ray *) take(n * 32); W.ray_next = (Y4Ray *) take(n * 32); W.pthr = (float *) take(n * 16); W.hit = (Y4Hit *) take(n * 16); W.hit0 = (Y4Hit *) take(n * 16);
 	W.sray = (Y4Ray *) take(2 * n * 32); W.shit = (Y4Hit *) take(2 * n * 16); W.scontrib = (float *) take(2 * n * 16);
+	W.ray0 = (Y4Ray *) take(n * 32); W.sw = (float *) take(n * 16);
 	W.pix = (uint32_t *) take(n * 4); W.samp = (uint32_t *) take(n * 4); W.flags = (uint32_t *) take(n * 4); W.lnum = (uint32_t *) take(n * 4);
 	L.q_hit0 = (uint32_t *) take(n * 4); L.q_path[0] = (uint32_t *) take(n * 4); L.q_path[1] = (uint32_t *) take(n * 4); L.q_shadow = (uint32_t *) take(2 * n * 4);
 	L.cap = cap;
@@ -323,7 +336,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	if(params->bounces < 1 || params->bounces > 11) { ctx->err = "bounces must be 1..11 (sample dimensions 4*depth+4 < 50)"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(params->path_samples < 0 || params->width < 1 || params->height < 1) { ctx->err = "bad path_samples / film size"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_mat; ++i)
-		if(mats[i].type != Y4GPU_MAT_SHINYDIFFUSE && mats[i].type != Y4GPU_MAT_LIGHT) { ctx->err = "unsupported material type"; return Y4GPU_ERR_UNSUPPORTED; }
+		if(mats[i].type < Y4GPU_MAT_SHINYDIFFUSE || mats[i].type > Y4GPU_MAT_MIRROR) { ctx->err = "unsupported material type"; return Y4GPU_ERR_UNSUPPORTED; }
 	for(uint32_t i = 0; i < n_mat; ++i)
 		if(mats[i].layer_count < 0 || (mats[i].layer_count > 0 && (mats[i].layer_first < 0 || !ctx->pt || (uint32_t) (mats[i].layer_first + mats[i].layer_count) > ctx->pt->n_layers)))
 		{ ctx->err = "material refers to layers that were not set (call y4gpu_pt_set_textures first)"; return Y4GPU_ERR_ARG; }
@@ -342,6 +355,11 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	sc.cam = derive_camera(*cam);
 	sc.bounces = params->bounces; sc.n_paths = params->path_samples; sc.rr_min_bounces = params->russian_roulette_min_bounces;
 	sc.no_recursive = params->no_recursive; sc.transp_background = params->transp_background;
+	sc.raydepth = params->raydepth; sc.trace_caustics = params->trace_caustics; sc.transp_refracted_background = params->transp_refracted_background;
+	sc.has_specular = 0;
+	for(uint32_t m = 0; m < n_mat; ++m) if(mats[m].type == Y4GPU_MAT_MIRROR) sc.has_specular = 1;
+	// no_recursive makes a mirror hit start sub-paths AND recurse: two branches per vertex, which the linear ray-level chain does not cover
+	if(sc.has_specular && sc.no_recursive) { ctx->err = "no_recursive with mirror materials is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
@@ -517,13 +535,13 @@ int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out)
 		if(!pt->counters_read)
 		{
 			// queue lengths of the pass (copied to pinned memory before ev1): rays actually traced
-			uint64_t sum[4] = {0, 0, 0, 0};
+			uint64_t sum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 			for(const auto &ck : pt->counter_kinds)
 			{
 				const unsigned long long v = pt->h_counters[ck.first & 0x7fffffffu];
-				sum[ck.second & 3] += (ck.first >> 31) ? (uint32_t) (v >> 32) : (uint32_t) v;
+				sum[ck.second & 7] += (ck.first >> 31) ? (uint32_t) (v >> 32) : (uint32_t) v;
 			}
-			pt->stats.rays_closest = pt->dense_closest + sum[0]; pt->stats.rays_shadow = sum[1];
+			pt->stats.rays_closest = pt->dense_closest + sum[0] + sum[4]; pt->stats.rays_shadow = sum[1];
 			pt->stats.camera_hits = sum[2]; pt->stats.path_entries = sum[0] + sum[3];
 			if(pt->params.profile)
 			{
@@ -608,7 +626,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	const int max_ls = pt->max_light_samples;
 	// counter slots: [0..5] traversal visit counters (profile mode), then one per queue / trace launch
 	const uint64_t n_waves = total ? (total + wave_size - 1) / wave_size : 0;
-	const size_t per_wave = 4 + 2 * all_lk.size() + (size_t) sc.n_paths * (2 + ((size_t) sc.bounces + 1) * (4 + 2 * (size_t) max_ls));
+	const size_t per_wave = 4 + 2 * ((size_t) (sc.has_specular ? (sc.raydepth < 20 ? sc.raydepth : 20) : 0) + 1) + 2 * all_lk.size() + (size_t) sc.n_paths * (2 + ((size_t) sc.bounces + 1) * (4 + 2 * (size_t) max_ls));
 	const size_t need = 8 + n_waves * per_wave;
 	if(need > pt->counters_cap)
 	{
@@ -663,8 +681,8 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		Y4PtWave W = lane.wave;
 		W.n = (uint32_t) ((total - first) < wave_size ? (total - first) : wave_size);
 		const int grid = pt_grid(ctx, W.n);
-		StageArgs a = {0, -1, -1, -1, -1, 0, 0};
-		StageQueues Q = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+		StageArgs a = {0, -1, -1, -1, -1, 0, 0, 0};
+		StageQueues Q = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 		// camera rays -> closest hits -> camera-hit stage with the first light sample
 		Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, ns_local, shard_index, shard_count));
 		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, nullptr, nullptr); pt->dense_closest += W.n;
@@ -672,7 +690,20 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		new_queue_pair(2, 1, n_hit0, Q.sh_count);
 		Q.out_q = lane.q_hit0; Q.out_count = n_hit0; Q.sh_q = lane.q_shadow;
 		a.l = all_lk.empty() ? -1 : all_lk[0].first;
+		if(sc.has_specular && sc.raydepth > 0) { Q.spec_q = lane.q_path[0]; Q.spec_count = new_queue_count(4); }
 		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
+		// ray levels (recursiveRaytrace): rays that mirrors reflected are traced and go through the camera-hit stage again;
+		// their hits join the same hit0 / shadow queues, so everything below sees one set of integrate() vertices
+		for(int level = 1; Q.spec_q && level <= sc.raydepth && level < 20; ++level)
+		{
+			const uint32_t *in_q = Q.spec_q, *in_count = Q.spec_count;
+			Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray0, W.hit, W.n, in_q, in_count);
+			Q.in_q = in_q; Q.in_count = in_count;
+			Q.spec_q = lane.q_path[level & 1]; Q.spec_count = new_queue_count(4);
+			a.level = level;
+			Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
+		}
+		Q.in_q = nullptr; Q.in_count = nullptr; Q.spec_q = nullptr; Q.spec_count = nullptr; a.level = 0;
 		for(size_t j = 0; j < all_lk.size(); ++j)
 		{
 			Y4_PT_TRACE(shadow_kind, W.sray, W.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);

@@ -93,6 +93,12 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 		o.bsdf_flags = Y4_BSDF_EMIT;
 		return o;
 	}
+	if(m.type == Y4GPU_MAT_MIRROR)                         // MirrorMaterial ctor (material_glass.h:86-91): ref_col_ = r_col * ref_val
+	{
+		o.color = c3(m.color[0] * m.diffuse_reflect, m.color[1] * m.diffuse_reflect, m.color[2] * m.diffuse_reflect);
+		o.bsdf_flags = Y4_BSDF_SPECULAR;
+		return o;
+	}
 	o.color = c3(m.color[0], m.color[1], m.color[2]);
 	o.layer_first = m.layer_first; o.layer_count = m.layer_count; o.emit_strength = m.emit;
 	o.emit = c3(m.emit * m.color[0], m.emit * m.color[1], m.emit * m.color[2]);

@@ -76,6 +76,15 @@ Y4_HD float y4_oren_nayar(const Y4PtMaterial &m, const V3 wi, const V3 wo, const
 	return fminf(1.f, fmaxf(0.f, xadd(m.oren_a, xmul(xmul(xmul(m.oren_b, maxcos_f), sin_alpha), tan_beta))));
 }
 
+// Vec3::reflectDir (vector.h:255-260)
+Y4_HD V3 y4_reflect_dir(const V3 n, const V3 v)
+{
+	const float vn = xdot(v, n);
+	if(vn < 0.f) return xneg(v);
+	const float k = xmul(2.f, vn);
+	return v3(xsub(xmul(k, n.x), v.x), xsub(xmul(k, n.y), v.y), xsub(xmul(k, n.z), v.z));
+}
+
 // Material::sample -> returns scolor; wi, w, pdf, sampled (false == BsdfFlags::None) are outputs.
 // `w` is left untouched when nothing is sampled (the reference leaves its out-parameter alone too).
 Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, float s1, float s2, uint32_t flags,
@@ -83,6 +92,12 @@ Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, flo
 {
 	sampled = false; pdf = 0.f;
 	if(m.type == Y4GPU_MAT_LIGHT) { w = 0.f; return c3f(0.f); }
+	if(m.type == Y4GPU_MAT_MIRROR)                         // MirrorMaterial::sample (material_glass.cc:435-441): s.flags_ is not looked at
+	{
+		wi = y4_reflect_dir(sp.n, wo);
+		sampled = true; w = 1.f;
+		return cscale(m.color, xdiv(1.f, fabsf(xdot(sp.n, wi))));
+	}
 	const float cos_ng_wo = xdot(sp.ng, wo);
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
 	const uint32_t cflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;

@@ -31,6 +31,8 @@ struct Y4PtWave
 	Y4Ray *sray;           // [2n] shadow rays: slot 0 at [i], slot 1 at [n + i]
 	Y4Hit *shit;           // [2n]
 	float *scontrib;       // [2n*4]
+	Y4Ray *ray0;           // [n] ray_level > 0 (Y4_PF_SPEC): the reflected ray that reached the vertex integrate() works on
+	float *sw;             // [n*4] Y4_PF_SPEC: product of the reflection colours down the mirror chain (xyz), ray level (w, int bits)
 };
 
 struct Y4PtPass
@@ -230,31 +232,54 @@ Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 }
 
 // ---- step: camera-ray hit (integrate(), :126-171 up to the path loop) -----------------------------
-// returns true and fills `vx` when the camera ray hit a surface
-Y4_HD bool y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t &f, Y4Vertex &vx)
+// `level` = ray_level of this integrate() call: 0 for the camera ray (W.ray), > 0 for a ray reflected by mirrors (W.ray0;
+// f comes in with Y4_PF_SPEC).  Returns 0: background, 1: surface hit, `vx` filled, 2: the hit is a perfect mirror and the
+// reflected ray was written to W.ray0 (recursiveRaytrace -> specularReflect -> integrate at level + 1,
+// integrator_montecarlo.cc:868-964; the chain's colour factors are multiplied up front into W.sw and applied when the
+// pixel-sample is splatted: same factors as the reference's unwinding products, in the opposite order).
+Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int level, uint32_t &f, Y4Vertex &vx)
 {
 	const Y4Hit h = ld_hit(W.hit, i);
-	const Y4Ray r = ld_ray(W.ray, i);
+	const Y4Ray r = level > 0 ? ld_ray(W.ray0, i) : ld_ray(W.ray, i);
+	const uint32_t spec = level > 0 ? (uint32_t) Y4_PF_SPEC : 0u;
 	if(h.prim < 0)
 	{
-		const bool transp = sc.transp_background != 0;      // ray_level == 0
+		const bool transp = sc.transp_background != 0 && (level == 0 || sc.transp_refracted_background != 0);   // TiledIntegrator::background
 		const C3 bg = transp ? c3f(0.f) : sc.background;
 		st4(W.col, i, f4(bg.r, bg.g, bg.b, transp ? 0.f : 1.f));
-		f = 0u;
-		return false;
+		f = spec;
+		return 0;
 	}
 	st_hit(W.hit0, i, h);
 	vx = y4_vertex(sc, r, h);
+	if((vx.m.bsdf_flags & Y4_BSDF_SPECULAR) && level + 1 <= sc.raydepth && level + 1 < 20)
+	{
+		// MirrorMaterial::getSpecular (material_glass.cc:443-451) + specularReflect
+		const V3 dir = y4_reflect_dir(y4_face_forward(vx.sp.ng, vx.sp.n, vx.wo), vx.wo);
+		C3 w = vx.m.color;
+		if(level > 0) w = cmul(ld3(W.sw, i), w);
+		st_ray(W.ray0, i, y4_mk_ray(vx.sp.p, sc.ray_min_dist, dir, -1.f));
+		st4(W.sw, i, f4(w.r, w.g, w.b, y4_u2f((uint32_t) (level + 1))));
+		f = Y4_PF_SPEC;
+		return 2;
+	}
 	C3 col = c3f(0.f);
 	if(vx.m.bsdf_flags & Y4_BSDF_EMIT) col = cadd(col, y4_mat_emit(vx.m, vx.sp, vx.wo));
 	st4(W.col, i, f4(col.r, col.g, col.b, 1.f));               // recursiveRaytrace: alpha_count == 0 -> alpha 1
 	st3(W.pcol, i, c3f(0.f));
 	st4(W.lsamp, i, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
-	f = Y4_PF_HIT0;
+	f = Y4_PF_HIT0 | spec;
 	if(vx.m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
 	const uint32_t path_flags = sc.no_recursive ? (uint32_t) Y4_BSDF_ALL : (uint32_t) Y4_BSDF_DIFFUSE;
 	if(sc.n_paths > 0 && (vx.m.bsdf_flags & path_flags)) f |= Y4_PF_PATHS;       // n_paths == 0: DirectLightIntegrator (integrator_direct_light.cc:94-143)
-	return true;
+	return 1;
+}
+
+// the ray integrate() was called with for this pixel-sample: the camera ray (recomputed, cheaper than a 32-byte read) or the
+// stored reflected ray
+Y4_HD Y4Ray y4_level_ray(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t f, uint32_t pix, uint32_t samp)
+{
+	return (f & Y4_PF_SPEC) ? ld_ray(W.ray0, i) : y4_primary_ray(sc, ps, pix, samp);
 }
 
 // number of samples doLightEstimation takes from light L (integrator_montecarlo.cc:396)
@@ -420,8 +445,10 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 	if(depth == 0)
 	{
 		if(m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIFF1; else f &= ~(uint32_t) Y4_PF_DIFF1;
-		if(m.bsdf_flags & Y4_BSDF_EMIT) emit = y4_mat_emit(m, vx.sp, vx.wo);
+		if(m.bsdf_flags & Y4_BSDF_EMIT) { emit = y4_mat_emit(m, vx.sp, vx.wo); f |= Y4_PF_EMIT1; } else f &= ~(uint32_t) Y4_PF_EMIT1;
 		direct = m.is_diffuse != 0;     // a non-diffuse vertex evaluates to exactly 0 for every light sample
+		// neither flag: no later vertex of this sub-path can add anything (light estimates need DIFF1, emission EMIT1)
+		if(!(f & (Y4_PF_DIFF1 | Y4_PF_EMIT1))) return 0;
 	}
 	else
 	{
@@ -435,6 +462,8 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 			if(probability <= 0.f || probability < random_value) return 0;
 			thr = cscale(thr, xdiv(1.f, probability));
 		}
+		// emission seen through a specular bounce; the flag tested is the FIRST path vertex's (mat_bsd_fs is not updated in the loop)
+		if((f & Y4_PF_EMIT1) && (f & Y4_PF_CAUSTIC)) emit = y4_mat_emit(m, vx.sp, vx.wo);
 	}
 	if(sc.n_lights == 0) direct = false;
 	if(!direct) return 1;
@@ -456,19 +485,22 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 // ==== fused wavefront stages ===========================================================================
 // Each returns a push mask: bit 0/1 = shadow-ray slot 0/1 written, bit 2 = the path goes on the stage's
 // output path queue.  y4_pt.cu runs them as kernels over compacted index queues; tests/emu as loops.
-enum : uint32_t { Y4_PUSH_S0 = 1u, Y4_PUSH_S1 = 2u, Y4_PUSH_PATH = 4u };
+enum : uint32_t { Y4_PUSH_S0 = 1u, Y4_PUSH_S1 = 2u, Y4_PUSH_PATH = 4u, Y4_PUSH_SPEC = 8u };
 
 // camera-ray hit + first direct-light sample (light l0, k = 0; l0 < 0: scene without lights).
 // Output queue: paths that hit a surface and have more to do (more light samples or sub-paths).
-Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l0)
+// level > 0: the same for a ray that mirrors reflected (bit 3 of the result: reflected again -> the ray-level queue).
+Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l0, int level)
 {
-	uint32_t f; Y4Vertex vx;
+	uint32_t f = 0u; Y4Vertex vx;
 	uint32_t push = 0u;
-	if(y4_pt_primary(sc, W, i, f, vx))
+	const int what = y4_pt_primary(sc, W, i, level, f, vx);
+	if(what == 1)
 	{
 		if(l0 >= 0) push |= y4_pt_direct(sc, W, ps, i, f, true, l0, 0, vx, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
 		if(f & (Y4_PF_DIRECT | Y4_PF_PATHS)) push |= Y4_PUSH_PATH;
 	}
+	else if(what == 2) push |= Y4_PUSH_SPEC;
 	W.flags[i] = f;
 	return push;
 }
@@ -483,7 +515,7 @@ Y4_HD uint32_t y4_stage_direct_step(const Y4PtScene &sc, const Y4PtWave &W, cons
 	int ll, ns;
 	if(y4_direct_active(sc, W, i, f, all_lights, l, k, ll, ns))
 	{
-		const Y4Ray r = all_lights ? y4_primary_ray(sc, ps, W.pix[i], W.samp[i]) : ld_ray(W.ray, i);
+		const Y4Ray r = all_lights ? y4_level_ray(sc, W, ps, i, f, W.pix[i], W.samp[i]) : ld_ray(W.ray, i);
 		const Y4Vertex vx = y4_vertex(sc, r, all_lights ? ld_hit(W.hit0, i) : ld_hit(W.hit, i));
 		push = y4_pt_direct(sc, W, ps, i, f, all_lights, l, k, vx, cache);
 	}
@@ -498,11 +530,11 @@ Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 	const uint32_t pix = W.pix[i], samp = W.samp[i];
 	const Y4Hit h = ld_hit(W.hit0, i);
 	if(l_last >= 0) y4_pt_direct_resolve(sc, W, i, f, true, l_last, k_last);
-	f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIFF1 | Y4_PF_DIRECT);
+	f &= ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIFF1 | Y4_PF_DIRECT | Y4_PF_EMIT1 | Y4_PF_CAUSTIC);
 	bool go = false;
 	if(f & Y4_PF_PATHS)
 	{
-		const Y4Vertex vx = y4_vertex(sc, y4_primary_ray(sc, ps, pix, samp), h);
+		const Y4Vertex vx = y4_vertex(sc, y4_level_ray(sc, W, ps, i, f, pix, samp), h);
 		C3 thr = c3f(0.f); Y4Ray out;
 		go = y4_bounce_sample<true>(sc, ps, pix, samp, 0, sub, vx, thr, out);
 		st3(W.thr, i, thr);
@@ -558,6 +590,8 @@ Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtP
 	{
 		Y4Ray out;
 		go = y4_bounce_sample<false>(sc, ps, pix, samp, depth + 1, sub, vx, thr, out);
+		// caustic = trace_caustics_ && sampled_flags has Specular | Glossy | Filter (:227): only the mirror samples such a lobe
+		if(go && sc.trace_caustics && (vx.m.bsdf_flags & Y4_BSDF_SPECULAR)) f |= Y4_PF_CAUSTIC; else f &= ~(uint32_t) Y4_PF_CAUSTIC;
 		if(go) { st_ray(W.ray_next, i, out); st3(W.thr, i, thr); }
 		else if(f & Y4_PF_DIRECT) st_ray(W.ray_next, i, y4_null_ray());
 	}
@@ -582,6 +616,7 @@ Y4_HD void y4_pt_finish_splat(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 	C3 col = c3(col4.x, col4.y, col4.z);
 	float alpha = col4.w;
 	if(f & Y4_PF_PATHS) col = cadd(col, cdiv(ld3(W.pcol, i), (float) (sc.n_paths > 1 ? sc.n_paths : 1)));
+	if(f & Y4_PF_SPEC) col = cmul(col, ld3(W.sw, i));               // specularReflect: integ.first *= reflect_data->col_, every level
 	if(alpha > 1.f) alpha = 1.f;
 	if(sc.clamp_samples > 0.f)      // Rgb::clampProportionalRgb (color.h:415-445)
 	{

@@ -100,6 +100,8 @@ struct Y4PtScene
 	Y4PtCamera cam;
 	// integrator
 	int bounces, n_paths, rr_min_bounces, no_recursive, transp_background;
+	int raydepth, trace_caustics, transp_refracted_background;
+	int has_specular;               // some material needs the ray-level loop (recursiveRaytrace)
 	C3 background;
 	float shadow_bias; int shadow_bias_auto;
 	float ray_min_dist; int ray_min_dist_auto;
@@ -140,5 +142,9 @@ enum : uint32_t
 	Y4_PF_DIRECT = 16u,          // the current vertex wants a one-light estimate this depth
 	Y4_PF_S0 = 32u, Y4_PF_S1 = 64u,  // shadow-ray slot 0/1 of the current light sample was traced
 	Y4_PF_C1 = 128u,             // W.scontrib slot 1 (the BSDF-sampled MIS estimator) holds a non-zero contribution; unset: it is zero and was not stored
-	Y4_PF_LCOL = 256u            // W.lcol holds non-zero emission picked up at the current vertex; unset: zero, not stored
+	Y4_PF_LCOL = 256u,           // W.lcol holds non-zero emission picked up at the current vertex; unset: zero, not stored
+	Y4_PF_SPEC = 512u,           // the vertex integrate() works on was reached through mirrors (ray_level > 0): W.ray0 is the ray
+	                             // into it, W.sw the product of the reflection colours (xyz) and the ray level (w)
+	Y4_PF_EMIT1 = 1024u,         // first path vertex's material has Emit (mat_bsd_fs, integrator_path_tracer.cc:196,256)
+	Y4_PF_CAUSTIC = 2048u        // the ray into the current path vertex was sampled from a specular lobe and caustic_type traces them
 };

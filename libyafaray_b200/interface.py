@@ -212,6 +212,8 @@ class Interface:
                     raise Y4Error(f"shinydiffusemat '{name}': shader slot '{k}' is not supported by the GPU back end (diffuse_shader only)")
             if "diffuse_shader" in p:
                 p["_diffuse_chain"] = self._diffuse_chain(name, p, [dict(e) for e in self.eparams])
+        elif t == "mirror":            # MirrorMaterial::factory reads `color` and `reflect` only (material_glass.cc:453-461)
+            p = {"type": "mirror", "color": p.get("color", (1.0, 1.0, 1.0, 1.0)), "reflect": p.get("reflect", 1.0)}
         elif t != "light_mat":
             raise Y4Error(f"material type '{t}' is not supported by the GPU back end")
         self.materials[name] = p
@@ -513,6 +515,8 @@ class Interface:
             m.receive_shadows, m.flat_material = int(p.get("receive_shadows", True)), int(p.get("flat_material", False))
             if p["type"] == "light_mat":
                 m.type, m.emit, m.double_sided = _lib.MAT_LIGHT, float(p.get("power", 1.0)), int(p.get("double_sided", False))
+            elif p["type"] == "mirror":
+                m.type, m.diffuse_reflect = _lib.MAT_MIRROR, float(p.get("reflect", 1.0))
             else:
                 m.type, m.diffuse_reflect, m.emit = _lib.MAT_SHINYDIFFUSE, float(p.get("diffuse_reflect", 1.0)), float(p.get("emit", 0.0))
                 if p.get("diffuse_brdf", "lambert") == "oren_nayar":
@@ -559,6 +563,10 @@ class Interface:
             pr.bounces, pr.path_samples = 1, 0
         pr.russian_roulette_min_bounces, pr.no_recursive = int(integ.get("russian_roulette_min_bounces", 0)), int(integ.get("no_recursive", False))
         pr.transp_background = int(integ.get("bg_transp", False))
+        if pr.no_recursive and any(self.materials[n]["type"] == "mirror" for n in mat_names):
+            raise Y4Error("no_recursive with mirror materials is not supported by the GPU back end")
+        pr.raydepth, pr.transp_refracted_background = int(integ.get("raydepth", 5)), int(integ.get("bg_transp_refract", False))
+        pr.trace_caustics = int(integ.get("type") == "pathtracing" and integ.get("caustic_type", "path") not in ("none", "photon"))
         pr.transp_shadows, pr.shadow_depth = int(bool(integ.get("transpShad", False))), int(integ.get("shadowDepth", 4))
         if bg is not None:
             c, pw = bg.get("color", (0.0, 0.0, 0.0, 1.0)), np.float32(bg.get("power", 1.0))

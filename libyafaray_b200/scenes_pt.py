@@ -81,19 +81,30 @@ def _uv_sphere(centre, radius, nu, nv):
 
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
-                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None):
+                oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None,
+                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
-    extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front."""
+    extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front.
+    mirror: {"objects": subset of ("tall", "short", "back", "left", "sphere"), "color": rgb, "reflect": r} -> those objects get a
+    `mirror` material; integrator_extra: integrator parameters set after the defaults (raydepth, caustic_type, ...)."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
     _material(api, "white", white, **extra)
     _material(api, "red", red, **extra)
-    _material(api, "green", green, **extra)
+    _material(api, "green", green, **({**extra, "emit": glow} if glow else extra))       # glow: the right wall also emits
     api.paramsClearAll()
     api.paramsSetString("type", "light_mat")
     api.paramsSetColor("color", 1.0, 0.85, 0.6, 1.0)
     api.paramsSetFloat("power", 18.0)
     api.createMaterial("emitter")
+    mirrored = set((mirror or {}).get("objects", ()))
+    if mirror:
+        api.paramsClearAll()
+        api.paramsSetString("type", "mirror")
+        api.paramsSetColor("color", *mirror.get("color", (0.9, 0.9, 0.9)), 1.0)
+        api.paramsSetFloat("reflect", mirror.get("reflect", 1.0))
+        api.createMaterial("mirror")
+    mat = lambda obj, default: "mirror" if obj in mirrored else default
 
     api.startGeometry()
     v, t = _quad((0, 0, 0), (1, 0, 0), (1, 0, 1), (0, 0, 1))
@@ -101,15 +112,15 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     v, t = _quad((0, 1, 0), (0, 1, 1), (1, 1, 1), (1, 1, 0))
     _mesh(api, "b_ceiling", "white", v, t)
     v, t = _quad((0, 0, 1), (1, 0, 1), (1, 1, 1), (0, 1, 1))
-    _mesh(api, "c_back", "white", v, t)
+    _mesh(api, "c_back", mat("back", "white"), v, t)
     v, t = _quad((0, 0, 0), (0, 0, 1), (0, 1, 1), (0, 1, 0))
-    _mesh(api, "d_left", "red", v, t)
+    _mesh(api, "d_left", mat("left", "red"), v, t)
     v, t = _quad((1, 0, 0), (1, 1, 0), (1, 1, 1), (1, 0, 1))
     _mesh(api, "e_right", "green", v, t)
     v, t = _box((0.53, 0.0, 0.53), (0.83, 0.6, 0.83), 18.0, (0.68, 0.0, 0.68))
-    _mesh(api, "f_tall", "white", v, t)
+    _mesh(api, "f_tall", mat("tall", "white"), v, t)
     v, t = _box((0.18, 0.0, 0.2), (0.48, 0.3, 0.5), -17.0, (0.33, 0.0, 0.35))
-    _mesh(api, "g_short", "white", v, t)
+    _mesh(api, "g_short", mat("short", "white"), v, t)
     # emitting quad just below the ceiling, facing down; the area light shares its corners
     lx0, lx1, lz0, lz1, ly = 0.37, 0.63, 0.395, 0.605, 0.999
     if not point_light:
@@ -117,7 +128,7 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         _mesh(api, "h_lamp", "emitter", v, t)
     if smooth_sphere is not None:       # a sphere on the short box, shaded with yafaray_smoothMesh(angle)
         v, t = _uv_sphere((0.33, 0.42, 0.35), 0.12, 12, 7)
-        _mesh(api, "i_sphere", "white", v, t)
+        _mesh(api, "i_sphere", mat("sphere", "white"), v, t)
         api.smoothMesh("i_sphere", float(smooth_sphere))
     api.endGeometry()
 
@@ -195,7 +206,7 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
 
     api.paramsClearAll()
     api.paramsSetString("type", "constant")
-    api.paramsSetColor("color", 0.0, 0.0, 0.0, 1.0)
+    api.paramsSetColor("color", *background, 1.0)
     api.createBackground("bg")
 
     api.paramsClearAll()
@@ -205,6 +216,7 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     api.paramsSetInt("russian_roulette_min_bounces", bounces if rr_min_bounces is None else rr_min_bounces)
     api.paramsSetString("caustic_type", "none")
     api.paramsSetInt("raydepth", 2)
+    _set_params(api, integrator_extra)
     api.createIntegrator("pt")
 
     api.paramsClearAll()

@@ -105,6 +105,9 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	sc.cam = derive_camera(*cam);
 	sc.bounces = params->bounces; sc.n_paths = params->path_samples; sc.rr_min_bounces = params->russian_roulette_min_bounces;
 	sc.no_recursive = params->no_recursive; sc.transp_background = params->transp_background;
+	sc.raydepth = params->raydepth; sc.trace_caustics = params->trace_caustics; sc.transp_refracted_background = params->transp_refracted_background;
+	sc.has_specular = 0;
+	for(uint32_t m = 0; m < n_mat; ++m) if(mats[m].type == Y4GPU_MAT_MIRROR) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
@@ -132,12 +135,14 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	if(n == 0) return 0;
 	std::vector<uint32_t> pix(n), samp(n), fl(n), lnum(n);
 	std::vector<float4> col(n), pcol(n), thr(n), pthr(n), lcol(n), acc_a(n), acc_b(n), lsamp(n), scontrib(2ull * n);
-	std::vector<Y4Ray> ray(n), ray2(n), sray(2ull * n);
+	std::vector<Y4Ray> ray(n), ray2(n), sray(2ull * n), ray0(n);
+	std::vector<float4> sw(n);
 	std::vector<Y4Hit> hit(n), hit0(n), shit(2ull * n);
 	Y4PtWave W;
 	W.n = n; W.pix = pix.data(); W.samp = samp.data(); W.flags = fl.data(); W.lnum = lnum.data();
 	W.col = &col[0].x; W.pcol = &pcol[0].x; W.thr = &thr[0].x; W.lcol = &lcol[0].x; W.acc_a = &acc_a[0].x; W.acc_b = &acc_b[0].x; W.lsamp = &lsamp[0].x; W.pthr = &pthr[0].x;
 	W.ray = ray.data(); W.ray_next = ray2.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = &scontrib[0].x;
+	W.ray0 = ray0.data(); W.sw = &sw[0].x;
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
 	for(uint32_t i = 0; i < n; ++i) { pix[i] = pixel_list ? pixel_list[i / ns_local] : i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
 	const int shadow_kind = params->transp_shadows ? Y4_TRACE_TSHADOW : Y4_TRACE_SHADOW;
@@ -148,7 +153,21 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	for(int l = 0; l < sc.n_lights; ++l)
 		for(int k = 0; k < y4_light_num_samples(sc, hl[l]); ++k) all_lk.push_back(std::make_pair(l, k));
 	std::vector<uint32_t> q_hit0, q_shadow, q_cur, q_next;
-	for(uint32_t i = 0; i < n; ++i) push(y4_stage_primary(sc, W, ps, i, all_lk.empty() ? -1 : all_lk[0].first), i, n, &q_hit0, &q_shadow);
+	const int l0 = all_lk.empty() ? -1 : all_lk[0].first;
+	std::vector<uint32_t> q_spec, q_spec_next;
+	auto primary = [&](uint32_t i, int level)
+	{
+		const uint32_t p = y4_stage_primary(sc, W, ps, i, l0, level);
+		push(p, i, n, &q_hit0, &q_shadow);
+		if(p & Y4_PUSH_SPEC) q_spec_next.push_back(i);
+	};
+	for(uint32_t i = 0; i < n; ++i) primary(i, 0);
+	for(int level = 1; sc.has_specular && level <= sc.raydepth && level < 20; ++level)      // ray levels, as y4gpu_pt_render_pass
+	{
+		q_spec.swap(q_spec_next); q_spec_next.clear();
+		trace(bvh, Y4_TRACE_CLOSEST, W.ray0, q_spec.data(), q_spec.size(), W.hit);
+		for(uint32_t i : q_spec) primary(i, level);
+	}
 	for(size_t j = 0; j < all_lk.size(); ++j)
 	{
 		trace(bvh, shadow_kind, W.sray, q_shadow.data(), q_shadow.size(), W.shit);

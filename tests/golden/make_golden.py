@@ -8,6 +8,7 @@ from /root/reference by `make -C oracle ref`).  Run in the build container only:
                         shadow and diffuse batches with the reference kd-tree's hit records
   rays_soup.npz      <- same on scenes.triangle_soup(3000) with incoherent + segment rays
   pt_dof.npz         <- the same harness on the Cornell box with a lens (PT_GOLDEN_DOF)
+  pt_mirror.npz      <- the same harness on the Cornell box with `mirror` materials (PT_GOLDEN_MIRROR)
   pt_lights.npz      <- the same harness on the Cornell box with directional / sun / sphere lights (PT_GOLDEN_LIGHTS)
   pt_city.npz        <- the same harness on scenes_pt.city (instanced buildings) for PT_GOLDEN_CITY
   pt_test01.npz      <- the same harness on scenes_pt.test01 (the reference's tests/test01 scene: image textures) for PT_GOLDEN_TEST01
@@ -69,6 +70,21 @@ PT_GOLDEN_LIGHTS = {
 }
 
 
+# `mirror` materials: the ray-level loop of recursiveRaytrace / specularReflect, specular bounces inside paths,
+# emission seen through them (caustic_type path), transparent background behind reflections -> pt_mirror.npz
+_MIRROR = dict(objects=("tall", "back"), color=(0.9, 0.95, 0.8), reflect=0.95)
+PT_GOLDEN_MIRROR = {
+    "mirror_box_and_wall": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, mirror=_MIRROR, integrator_extra=dict(raydepth=3, caustic_type="path")),
+    "mirror_glow_caustic_paths": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, mirror=_MIRROR, glow=0.7, path_samples=2, light_samples=2,
+                                      integrator_extra=dict(raydepth=2, caustic_type="path")),
+    "mirror_hall_raydepth8": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, point_light=True, filter_type="gauss",
+                                  mirror=dict(objects=("tall", "back", "left", "short")), integrator_extra=dict(raydepth=8, caustic_type="path")),
+    "mirror_sphere_transp_bg_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", smooth_sphere=180.0,
+                                           mirror=dict(objects=("sphere", "short")), background=(0.3, 0.2, 0.1),
+                                           integrator_extra=dict(raydepth=2, bg_transp=True, bg_transp_refract=True)),
+}
+
+
 # C1 (BASELINE configs[0]): the reference's tests/test01 scene -- six cubes with image textures (layer + cube-mapped
 # texture_mapper nodes on orco coordinates) -- with the path tracer, as shipped (directlighting), and variants that walk
 # through the other texture / mapper / layer modes -> pt_test01.npz.  The reference build here has the TGA and HDR
@@ -122,6 +138,7 @@ def make_city():
     make_extra(PT_GOLDEN_CITY, "pt_city.npz")
     make_extra(PT_GOLDEN_DOF, "pt_dof.npz")
     make_extra(PT_GOLDEN_LIGHTS, "pt_lights.npz")
+    make_extra(PT_GOLDEN_MIRROR, "pt_mirror.npz")
     make_test01()
 
 

@@ -13,10 +13,11 @@ from libyafaray_b200 import interface, scenes_pt
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 sys.path.insert(0, GOLD)
-from make_golden import PT_GOLDEN, PT_GOLDEN_CITY, PT_GOLDEN_DOF, PT_GOLDEN_LIGHTS, PT_GOLDEN_TEST01, TEST01_DIR  # noqa: E402
+from make_golden import PT_GOLDEN, PT_GOLDEN_CITY, PT_GOLDEN_DOF, PT_GOLDEN_LIGHTS, PT_GOLDEN_MIRROR, PT_GOLDEN_TEST01, TEST01_DIR  # noqa: E402
 
 ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: ("pt_city.npz", v) for k, v in PT_GOLDEN_CITY.items()},
               **{k: ("pt_dof.npz", v) for k, v in PT_GOLDEN_DOF.items()}, **{k: ("pt_test01.npz", v) for k, v in PT_GOLDEN_TEST01.items()},
+              **{k: ("pt_mirror.npz", v) for k, v in PT_GOLDEN_MIRROR.items()},
               # several lights + path tracing: light choice numbering differs from the reference's thread-dependent counter
               # (DESIGN.md), those are checked against the CPU emulation below and the emulation against the golden image
               **{k: ("pt_lights.npz", v) for k, v in PT_GOLDEN_LIGHTS.items() if v.get("integrator") == "directlighting"}}
