@@ -151,7 +151,11 @@ typedef struct y4gpu_pt_material
 	int32_t flat_material;        /* default 0 */
 	int32_t layer_first, layer_count;   /* shinydiffusemat `diffuse_shader`: its chain of layer nodes in y4gpu_pt_set_textures'
 	                                       layer array, bottom layer first (layer_count == 0: plain `color`) */
-	int32_t reserved[3];
+	float specular_reflect;       /* shinydiffusemat `specular_reflect` (default 0): strength of the perfect-mirror component */
+	float mirror_color[3];        /* shinydiffusemat `mirror_color` (default 1 1 1) */
+	int32_t fresnel_effect;       /* shinydiffusemat `fresnel_effect`: the mirror component is weighted by the Fresnel term of `ior` */
+	float ior;                    /* shinydiffusemat `IOR` (default 1.33) */
+	int32_t reserved[2];
 } y4gpu_pt_material;
 
 /* Image textures and the `diffuse_shader` node chains of shinydiffusemat: texture_mapper + layer nodes

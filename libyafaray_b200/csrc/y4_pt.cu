@@ -38,7 +38,7 @@ struct Y4Pt
 		uint32_t cap = 0;
 		Y4PtWave wave = {};
 		void *mem = nullptr;
-		uint32_t *q_hit0 = nullptr, *q_path[2] = {nullptr, nullptr}, *q_shadow = nullptr;   // index queues (in mem)
+		uint32_t *q_hit0 = nullptr, *q_path[2] = {nullptr, nullptr}, *q_shadow = nullptr, *q_spec[2] = {nullptr, nullptr};   // index queues (in mem)
 		cudaStream_t stream = nullptr;      // lane 0: the context's stream; lane 1: own stream, forked/joined per pass
 		cudaEvent_t done = nullptr;
 	} lanes[kMaxLanes];
@@ -77,7 +77,7 @@ namespace {
 
 constexpr int kPtThreads = 256;
 
-enum { kStPrimary, kStDirectStep, kStStart, kStPath };
+enum { kStPrimary, kStDirectStep, kStStart, kStPath, kStLevelFinish };
 struct StageArgs { int all_lights, l_prev, k_prev, l, k, depth, sub, level; };
 struct StageQueues
 {
@@ -116,10 +116,12 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 			if(STAGE == kStPrimary) push = y4_stage_primary(sc, W, ps, i, a.l, a.level);
 			else if(STAGE == kStDirectStep) push = y4_stage_direct_step(sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
 			else if(STAGE == kStStart) push = y4_stage_start(sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
+			else if(STAGE == kStLevelFinish) push = y4_stage_level_finish(sc, W, ps, i, a.level);
 			else push = y4_stage_path(sc, W, ps, i, a.depth, a.sub, a.k_prev);
 		}
 		// queue appends: one atomic per warp; when a stage feeds both queues their two 32-bit lengths share one 64-bit
 		// counter slot (path count low, shadow count high) and a single 64-bit atomic reserves both ranges
+		if(STAGE == kStLevelFinish) push &= Y4_PUSH_SPEC;
 		const uint32_t m0 = (STAGE != kStStart) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_S0) : 0u;
 		const uint32_t m1 = (STAGE != kStStart) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_S1) : 0u;
 		const uint32_t mp = (STAGE != kStDirectStep) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH) : 0u;
@@ -146,7 +148,7 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 			if(push & Y4_PUSH_S1) Q.sh_q[at_sh + __popc(m0) + __popc(m1 & lt_mask)] = W.n + i;
 			if(push & Y4_PUSH_PATH) Q.out_q[at_p + __popc(mp & lt_mask)] = i;
 		}
-		if(STAGE == kStPrimary && Q.spec_q)
+		if((STAGE == kStPrimary || STAGE == kStLevelFinish) && Q.spec_q)
 		{
 			const uint32_t ms = __ballot_sync(0xffffffffu, push & Y4_PUSH_SPEC);
 			if(ms)
@@ -207,7 +209,7 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt::Lane &L, uint32_t cap)
 	if(cap <= L.cap) return Y4GPU_OK;
 	pt_free_wave(L);
 	const size_t n = cap;
-	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 16 /*pthr*/ + 2 * 32 + 16 + 16 /*ray x2 hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/ + 32 + 16 /*ray0 sw*/
+	const size_t bytes = n * (4 * 4 /*pix samp flags lnum*/ + 6 * 16 /*col pcol thr lcol acc_a acc_b*/ + 16 /*pthr*/ + 2 * 32 + 16 + 16 /*ray x2 hit hit0*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/ + 32 + 16 + 16 + 8 /*ray0 sw acc q_spec*/
 	                          + 16 /*lsamp*/ + 5 * 4 /*queues*/) + 512;
 	Y4_CUDA(ctx, cudaMalloc(&L.mem, bytes));
 	char *p = (char *) L.mem;
@@ -217,7 +219,8 @@ int pt_alloc_wave(y4gpu_ctx *ctx, Y4Pt::Lane &L, uint32_t cap)
 	W.acc_a = (float *) take(n * 16); W.acc_b = (float *) take(n * 16); W.lsamp = (float *) take(n * 16);
 	W.ray = (Y4Ray *) take(n * 32); W.ray_next = (Y4Ray *) take(n * 32); W.pthr = (float *) take(n * 16); W.hit = (Y4Hit *) take(n * 16); W.hit0 = (Y4Hit *) take(n * 16);
 	W.sray = (Y4Ray *) take(2 * n * 32); W.shit = (Y4Hit *) take(2 * n * 16); W.scontrib = (float *) take(2 * n * 16);
-	W.ray0 = (Y4Ray *) take(n * 32); W.sw = (float *) take(n * 16);
+	W.ray0 = (Y4Ray *) take(n * 32); W.sw = (float *) take(n * 16); W.acc = (float *) take(n * 16);
+	L.q_spec[0] = (uint32_t *) take(n * 4); L.q_spec[1] = (uint32_t *) take(n * 4);
 	W.pix = (uint32_t *) take(n * 4); W.samp = (uint32_t *) take(n * 4); W.flags = (uint32_t *) take(n * 4); W.lnum = (uint32_t *) take(n * 4);
 	L.q_hit0 = (uint32_t *) take(n * 4); L.q_path[0] = (uint32_t *) take(n * 4); L.q_path[1] = (uint32_t *) take(n * 4); L.q_shadow = (uint32_t *) take(2 * n * 4);
 	L.cap = cap;
@@ -357,9 +360,13 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	sc.no_recursive = params->no_recursive; sc.transp_background = params->transp_background;
 	sc.raydepth = params->raydepth; sc.trace_caustics = params->trace_caustics; sc.transp_refracted_background = params->transp_refracted_background;
 	sc.has_specular = 0;
-	for(uint32_t m = 0; m < n_mat; ++m) if(mats[m].type == Y4GPU_MAT_MIRROR) sc.has_specular = 1;
+	for(uint32_t m = 0; m < n_mat; ++m)
+	{
+		if(mats[m].type == Y4GPU_MAT_MIRROR && !sc.has_specular) sc.has_specular = 1;
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].specular_reflect > 0.00001f) sc.has_specular = 2;
+	}
 	// no_recursive makes a mirror hit start sub-paths AND recurse: two branches per vertex, which the linear ray-level chain does not cover
-	if(sc.has_specular && sc.no_recursive) { ctx->err = "no_recursive with mirror materials is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
+	if(sc.has_specular && sc.no_recursive) { ctx->err = "no_recursive with mirror materials / specular_reflect is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
@@ -626,7 +633,9 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	const int max_ls = pt->max_light_samples;
 	// counter slots: [0..5] traversal visit counters (profile mode), then one per queue / trace launch
 	const uint64_t n_waves = total ? (total + wave_size - 1) / wave_size : 0;
-	const size_t per_wave = 4 + 2 * ((size_t) (sc.has_specular ? (sc.raydepth < 20 ? sc.raydepth : 20) : 0) + 1) + 2 * all_lk.size() + (size_t) sc.n_paths * (2 + ((size_t) sc.bounces + 1) * (4 + 2 * (size_t) max_ls));
+	const size_t n_levels = (size_t) (sc.has_specular ? (sc.raydepth < 20 ? sc.raydepth : 20) : 0) + 1;
+	const size_t per_level = 6 + 2 * all_lk.size() + (size_t) sc.n_paths * (2 + ((size_t) sc.bounces + 1) * (4 + 2 * (size_t) max_ls));
+	const size_t per_wave = sc.has_specular == 2 ? n_levels * per_level : per_level + 2 * n_levels;
 	const size_t need = 8 + n_waves * per_wave;
 	if(need > pt->counters_cap)
 	{
@@ -683,24 +692,40 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		const int grid = pt_grid(ctx, W.n);
 		StageArgs a = {0, -1, -1, -1, -1, 0, 0, 0};
 		StageQueues Q = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-		// camera rays -> closest hits -> camera-hit stage with the first light sample
-		Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, ns_local, shard_index, shard_count));
-		Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, nullptr, nullptr); pt->dense_closest += W.n;
+		// Ray levels (recursiveRaytrace).  Pure mirrors reflect inside the camera-hit step, so whole chains are followed before
+		// anything is estimated and their end points share one run of the estimate below.  A shinydiffuse vertex with a mirror
+		// component needs its own estimate first: then every level is one run (camera-hit step, estimate, level-finish stage).
+		const int max_level = (sc.has_specular && sc.raydepth > 0) ? (sc.raydepth < 19 ? sc.raydepth : 19) : 0;
+		const bool level_runs = sc.has_specular == 2;
+		uint32_t *next_level_count = nullptr;                    // length of the queue of rays reflected into `level + 1`
+		for(int level = 0; level <= (level_runs ? max_level : 0); ++level)
+		{
+		a = {0, -1, -1, -1, -1, 0, 0, level};
+		Q = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+		if(level == 0)
+		{
+			// camera rays -> closest hits -> camera-hit stage with the first light sample
+			Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, ns_local, shard_index, shard_count));
+			Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, nullptr, nullptr); pt->dense_closest += W.n;
+		}
+		else
+		{
+			Q.in_q = lane.q_spec[level & 1]; Q.in_count = next_level_count;
+			Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray0, W.hit, W.n, Q.in_q, Q.in_count);
+		}
 		uint32_t *n_hit0 = nullptr;
 		new_queue_pair(2, 1, n_hit0, Q.sh_count);
 		Q.out_q = lane.q_hit0; Q.out_count = n_hit0; Q.sh_q = lane.q_shadow;
 		a.l = all_lk.empty() ? -1 : all_lk[0].first;
-		if(sc.has_specular && sc.raydepth > 0) { Q.spec_q = lane.q_path[0]; Q.spec_count = new_queue_count(4); }
+		if(level < max_level) { Q.spec_q = lane.q_spec[(level + 1) & 1]; Q.spec_count = next_level_count = new_queue_count(4); }
 		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
-		// ray levels (recursiveRaytrace): rays that mirrors reflected are traced and go through the camera-hit stage again;
-		// their hits join the same hit0 / shadow queues, so everything below sees one set of integrate() vertices
-		for(int level = 1; Q.spec_q && level <= sc.raydepth && level < 20; ++level)
+		for(int lv = 1; !level_runs && lv <= max_level; ++lv)
 		{
 			const uint32_t *in_q = Q.spec_q, *in_count = Q.spec_count;
 			Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray0, W.hit, W.n, in_q, in_count);
 			Q.in_q = in_q; Q.in_count = in_count;
-			Q.spec_q = lane.q_path[level & 1]; Q.spec_count = new_queue_count(4);
-			a.level = level;
+			Q.spec_q = lv < max_level ? lane.q_spec[(lv + 1) & 1] : nullptr; Q.spec_count = lv < max_level ? new_queue_count(4) : nullptr;
+			a.level = lv;
 			Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
 		}
 		Q.in_q = nullptr; Q.in_count = nullptr; Q.spec_q = nullptr; Q.spec_count = nullptr; a.level = 0;
@@ -756,6 +781,13 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 			}
 		}
 		W.ray = ray_buf[0]; W.ray_next = ray_buf[1];
+		if(level_runs && level < max_level)
+		{
+			Q = {lane.q_hit0, n_hit0, nullptr, nullptr, nullptr, nullptr, lane.q_spec[(level + 1) & 1], next_level_count};
+			a.level = level;
+			Y4_PT_LAUNCH(3, launch_stage<kStLevelFinish>(stage_minb, grid, st, dsc, W, ps, a, Q));
+		}
+		}   // ray levels
 		Y4_PT_LAUNCH(5, k_pt_splat<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, pt->d_film_w, pt->d_film_rgba));
 		Y4_CUDA(ctx, cudaGetLastError());
 	}

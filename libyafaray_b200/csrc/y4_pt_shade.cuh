@@ -76,6 +76,29 @@ Y4_HD float y4_oren_nayar(const Y4PtMaterial &m, const V3 wi, const V3 wo, const
 	return fminf(1.f, fmaxf(0.f, xadd(m.oren_a, xmul(xmul(xmul(m.oren_b, maxcos_f), sin_alpha), tan_beta))));
 }
 
+// ShinyDiffuseMaterial::getFresnelKr (material_shiny_diffuse.cc:104-118)
+Y4_HD float y4_fresnel_kr(const Y4PtMaterial &m, const V3 wo, const V3 n)
+{
+	if(!m.fresnel) return 1.f;
+	const V3 nn = xdot(wo, n) < 0.f ? xneg(n) : n;
+	const float c = xdot(wo, nn);
+	float g = xsub(xadd(m.ior_squared, xmul(c, c)), 1.f);
+	g = g < 0.f ? 0.f : xsqrt(g);
+	const float aux = xmul(c, xadd(g, c));
+	const float gmc = xsub(g, c), gpc = xadd(g, c), am = xsub(aux, 1.f), ap = xadd(aux, 1.f);
+	return xmul(xdiv(xmul(xmul(0.5f, gmc), gmc), xmul(gpc, gpc)), xadd(1.f, xdiv(xmul(am, am), xmul(ap, ap))));
+}
+
+// ShinyDiffuseMaterial::accumulate (:123-134) for components {mirror, 0, 0, diffuse}: accum[0] and accum[3]
+Y4_HD void y4_shiny_accumulate(const Y4PtMaterial &m, const V3 wo, const V3 n, float &accum0, float &accum3)
+{
+	const float kr = y4_fresnel_kr(m, wo, n);
+	accum0 = xmul(m.is_mirror ? m.mirror_strength : 0.f, kr);
+	float acc = xsub(1.f, accum0);
+	acc = xmul(acc, xsub(1.f, 0.f)); acc = xmul(acc, xsub(1.f, 0.f));
+	accum3 = xmul(m.is_diffuse ? m.diffuse_strength : 0.f, acc);
+}
+
 // Vec3::reflectDir (vector.h:255-260)
 Y4_HD V3 y4_reflect_dir(const V3 n, const V3 v)
 {
@@ -88,32 +111,51 @@ Y4_HD V3 y4_reflect_dir(const V3 n, const V3 v)
 // Material::sample -> returns scolor; wi, w, pdf, sampled (false == BsdfFlags::None) are outputs.
 // `w` is left untouched when nothing is sampled (the reference leaves its out-parameter alone too).
 Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, float s1, float s2, uint32_t flags,
-                       V3 &wi, float &w, float &pdf, bool &sampled)
+                       V3 &wi, float &w, float &pdf, bool &sampled, bool &specular)
 {
-	sampled = false; pdf = 0.f;
+	sampled = false; pdf = 0.f; specular = false;
 	if(m.type == Y4GPU_MAT_LIGHT) { w = 0.f; return c3f(0.f); }
 	if(m.type == Y4GPU_MAT_MIRROR)                         // MirrorMaterial::sample (material_glass.cc:435-441): s.flags_ is not looked at
 	{
 		wi = y4_reflect_dir(sp.n, wo);
-		sampled = true; w = 1.f;
+		sampled = true; w = 1.f; specular = true;
 		return cscale(m.color, xdiv(1.f, fabsf(xdot(sp.n, wi))));
 	}
 	const float cos_ng_wo = xdot(sp.ng, wo);
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
-	const uint32_t cflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
-	float sum = 0.f, width = 0.f, val = 0.f;
-	int n_match = 0;
-	if(m.is_diffuse && (flags & cflags) == cflags) { width = m.diffuse_strength; sum = xadd(sum, width); val = sum; n_match = 1; }
-	if(!n_match || sum < 0.00001f) return c3f(1.f);
+	float accum0, accum3;
+	y4_shiny_accumulate(m, wo, n, accum0, accum3);
+	// components in c_flags_ order: perfect mirror (Specular | Reflect), then Lambert / Oren-Nayar (Diffuse | Reflect)
+	const uint32_t mflags = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT, dflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
+	// (scalars instead of the reference's val[] / width[] / choice[] arrays: same arithmetic, no local memory)
+	const bool mm = m.is_mirror && (flags & mflags) == mflags, dm = m.is_diffuse && (flags & dflags) == dflags;
+	float sum = 0.f, val_m = 0.f;
+	if(mm) { sum = xadd(sum, accum0); val_m = sum; }
+	if(dm) sum = xadd(sum, accum3);
+	if(!(mm || dm) || sum < 0.00001f) return c3f(1.f);
 	const float inv_sum = xdiv(1.f, sum);
-	val = xmul(val, inv_sum); width = xmul(width, inv_sum);
-	(void) val;                                                    // single component: pick == 0 either way
-	const float s_1 = xdiv(s1, width);
-	wi = y4_cos_hemisphere(n, sp.nu, sp.nv, s_1, s2);
+	const float wm = xmul(accum0, inv_sum), wd = xmul(accum3, inv_sum);
+	val_m = xmul(val_m, inv_sum);
+	// pick = first matched component with s1 <= val[i], else the last one
+	const bool pick_mirror = mm && (!dm || s1 <= val_m);
+	const float wpick = pick_mirror ? wm : wd;
+	const float s_1 = (!pick_mirror && mm) ? xdiv(xsub(s1, val_m), wpick) : xdiv(s1, wpick);
 	C3 scolor = c3f(0.f);
-	if(xmul(cos_ng_wo, xdot(sp.ng, wi)) > 0.f) scolor = cscale(m.color, m.diffuse_strength);   // accum_c[3] * colour
-	if(m.oren_nayar) scolor = cscale(scolor, y4_oren_nayar(m, wo, wi, n));
-	pdf = xmul(fabsf(xdot(wi, n)), width);
+	if(pick_mirror)
+	{
+		wi = y4_reflect_dir(n, wo);
+		pdf = wpick;
+		scolor = cscale(m.mirror_color, accum0);
+		scolor = cscale(scolor, xdiv(1.f, fmaxf(fabsf(xdot(sp.n, wi)), 1.0e-6f)));
+		specular = true;
+	}
+	else
+	{
+		wi = y4_cos_hemisphere(n, sp.nu, sp.nv, s_1, s2);
+		if(xmul(cos_ng_wo, xdot(sp.ng, wi)) > 0.f) scolor = cscale(m.color, accum3);
+		if(m.oren_nayar) scolor = cscale(scolor, y4_oren_nayar(m, wo, wi, n));
+		pdf = xmul(fabsf(xdot(wi, n)), wpick);
+	}
 	sampled = true;
 	w = xdiv(fabsf(xdot(wi, sp.n)), xadd(xmul(pdf, 0.99f), 0.01f));
 	w = xadd(xmul(w, 1.f), xmul(1.f, xsub(1.f, 1.f)));             // alpha == 1 for opaque materials
@@ -125,7 +167,9 @@ Y4_HD C3 y4_mat_eval(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, const
 	if(m.type == Y4GPU_MAT_LIGHT || !m.is_diffuse) return c3f(0.f);     // Material::eval default / no Diffuse flag
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
 	if(xdot(n, wl) < 0.f && !m.flat_material) return c3f(0.f);
-	float m_d = xmul(xmul(1.f, xsub(1.f, 0.f)), m.diffuse_strength);
+	const float kr = y4_fresnel_kr(m, wo, n);
+	const float m_t = xmul(xsub(1.f, xmul(kr, m.is_mirror ? m.mirror_strength : 0.f)), xsub(1.f, 0.f));
+	float m_d = xmul(xmul(m_t, xsub(1.f, 0.f)), m.diffuse_strength);
 	if(m.oren_nayar) m_d = xmul(m_d, y4_oren_nayar(m, wo, wl, n));
 	return cscale(m.color, m_d);
 }
@@ -134,8 +178,12 @@ Y4_HD float y4_mat_pdf(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, con
 {
 	if(m.type == Y4GPU_MAT_LIGHT || !m.is_diffuse) return 0.f;
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
-	const float width = m.diffuse_strength;
-	const float sum = xadd(0.f, width);
+	// bsdfs = Glossy | Diffuse | Dispersive | Reflect | Transmit hasAny() of both components' flags: the mirror's width counts in the sum
+	float accum0, width;
+	y4_shiny_accumulate(m, wo, n, accum0, width);
+	float sum = 0.f;
+	if(m.is_mirror) sum = xadd(sum, accum0);
+	sum = xadd(sum, width);
 	const float pdf = xadd(0.f, xmul(fabsf(xdot(wi, n)), width));
 	if(sum < 0.00001f) return 0.f;
 	return xdiv(pdf, sum);
@@ -366,9 +414,9 @@ Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtM
 	{
 		const float tmin_b = sc.ray_min_dist_auto ? xmul(sc.ray_min_dist, fmaxf(1.f, plen)) : sc.ray_min_dist;
 		V3 wi = v3(0.f, 0.f, 0.f);
-		float W = 0.f, s_pdf = 0.f; bool sampled;
+		float W = 0.f, s_pdf = 0.f; bool sampled, specular;
 		const uint32_t fl = Y4_BSDF_GLOSSY | Y4_BSDF_DIFFUSE | Y4_BSDF_DISPERSIVE | Y4_BSDF_REFLECT | Y4_BSDF_TRANSMIT;
-		const C3 surf = y4_mat_sample(m, sp, wo, s1, s2, fl, wi, W, s_pdf, sampled);
+		const C3 surf = y4_mat_sample(m, sp, wo, s1, s2, fl, wi, W, s_pdf, sampled, specular);
 		float t = 0.f, ipdf = 0.f; C3 lcol = c3f(0.f);
 		if(s_pdf > 1e-6f && y4_light_intersect(L, sp.p, wi, t, lcol, ipdf) && ipdf > 1e-6f)
 		{

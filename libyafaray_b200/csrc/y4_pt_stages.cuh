@@ -32,6 +32,7 @@ struct Y4PtWave
 	Y4Hit *shit;           // [2n]
 	float *scontrib;       // [2n*4]
 	Y4Ray *ray0;           // [n] ray_level > 0 (Y4_PF_SPEC): the reflected ray that reached the vertex integrate() works on
+	float *acc;            // [n*4] Y4_PF_ACC: radiance of the upper ray levels, already weighted
 	float *sw;             // [n*4] Y4_PF_SPEC: product of the reflection colours down the mirror chain (xyz), ray level (w, int bits)
 };
 
@@ -241,7 +242,7 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 {
 	const Y4Hit h = ld_hit(W.hit, i);
 	const Y4Ray r = level > 0 ? ld_ray(W.ray0, i) : ld_ray(W.ray, i);
-	const uint32_t spec = level > 0 ? (uint32_t) Y4_PF_SPEC : 0u;
+	const uint32_t spec = level > 0 ? (f & (uint32_t) (Y4_PF_SPEC | Y4_PF_ACC)) : 0u;      // f in: the flags the level above left
 	if(h.prim < 0)
 	{
 		const bool transp = sc.transp_background != 0 && (level == 0 || sc.transp_refracted_background != 0);   // TiledIntegrator::background
@@ -252,7 +253,8 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 	}
 	st_hit(W.hit0, i, h);
 	vx = y4_vertex(sc, r, h);
-	if((vx.m.bsdf_flags & Y4_BSDF_SPECULAR) && level + 1 <= sc.raydepth && level + 1 < 20)
+	const bool deeper = level + 1 <= sc.raydepth && level + 1 < 20;
+	if(vx.m.type == Y4GPU_MAT_MIRROR && deeper)
 	{
 		// MirrorMaterial::getSpecular (material_glass.cc:443-451) + specularReflect
 		const V3 dir = y4_reflect_dir(y4_face_forward(vx.sp.ng, vx.sp.n, vx.wo), vx.wo);
@@ -260,7 +262,7 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 		if(level > 0) w = cmul(ld3(W.sw, i), w);
 		st_ray(W.ray0, i, y4_mk_ray(vx.sp.p, sc.ray_min_dist, dir, -1.f));
 		st4(W.sw, i, f4(w.r, w.g, w.b, y4_u2f((uint32_t) (level + 1))));
-		f = Y4_PF_SPEC;
+		f = Y4_PF_SPEC | (spec & Y4_PF_ACC);
 		return 2;
 	}
 	C3 col = c3f(0.f);
@@ -269,6 +271,7 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 	st3(W.pcol, i, c3f(0.f));
 	st4(W.lsamp, i, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
 	f = Y4_PF_HIT0 | spec;
+	if(vx.m.is_mirror && deeper) f |= Y4_PF_RECURSE;
 	if(vx.m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
 	const uint32_t path_flags = sc.no_recursive ? (uint32_t) Y4_BSDF_ALL : (uint32_t) Y4_BSDF_DIFFUSE;
 	if(sc.n_paths > 0 && (vx.m.bsdf_flags & path_flags)) f |= Y4_PF_PATHS;       // n_paths == 0: DirectLightIntegrator (integrator_direct_light.cc:94-143)
@@ -395,7 +398,7 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 // FIRST: the vertex is the camera hit (bounce 0), else the vertex reached by bounce `depth - 1`.
 // thr: throughput at the vertex in, throughput along the new ray out.  Returns true when `out` is the next ray.
 template<bool FIRST>
-Y4_HD bool y4_bounce_sample(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp, int depth, int sub, const Y4Vertex &vx, C3 &thr, Y4Ray &out)
+Y4_HD bool y4_bounce_sample(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pix, uint32_t samp, int depth, int sub, const Y4Vertex &vx, C3 &thr, Y4Ray &out, bool &specular)
 {
 	const Y4PixelId s = y4_pixel_id(sc, ps, pix, samp);
 	const uint32_t offs = (uint32_t) sc.n_paths * s.sample + s.offset + (uint32_t) sub;
@@ -414,7 +417,7 @@ Y4_HD bool y4_bounce_sample(const Y4PtScene &sc, const Y4PtPass &ps, uint32_t pi
 	}
 	V3 wi = v3(0.f, 0.f, 1.f);
 	float w = 0.f, pdf; bool sampled;
-	C3 scol = y4_mat_sample(vx.m, vx.sp, vx.wo, s1, s2, sflags, wi, w, pdf, sampled);
+	C3 scol = y4_mat_sample(vx.m, vx.sp, vx.wo, s1, s2, sflags, wi, w, pdf, sampled, specular);
 	scol = cscale(scol, w);
 	if(FIRST) thr = scol;
 	else
@@ -440,7 +443,9 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 #ifdef Y4_TEST_LIGHT_CHOICE_HOOK
 	// tests/emu only: every estimateOneDirectLight call of the reference advances its counter, also the ones this
 	// function skips because they evaluate to exactly zero (non-diffuse vertex) or that Russian roulette discards later
-	if(sc.n_lights > 1 && (depth == 0 || (f & Y4_PF_DIFF1))) y4_test_light_choice_called(pix, samp, sub, depth);
+	// (the reference finishes all sub-paths of a ray level before it recurses: the level goes in front of the sub-path index)
+	const int lc_sub = sub + 4096 * ((f & Y4_PF_SPEC) ? (int) y4_f2u(ld4(W.sw, i).w) : 0);
+	if(sc.n_lights > 1 && (depth == 0 || (f & Y4_PF_DIFF1))) y4_test_light_choice_called(pix, samp, lc_sub, depth);
 #endif
 	if(depth == 0)
 	{
@@ -474,7 +479,7 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 	{
 		uint32_t corr = (pix * 1009u + ps.pass_offs + samp) * (uint32_t) (sc.bounces * sc.n_paths) + (uint32_t) (sub * sc.bounces + depth);
 #ifdef Y4_TEST_LIGHT_CHOICE_HOOK
-		corr = y4_test_light_choice(pix, samp, sub, depth, corr);   // tests/emu only: replays the reference's single-thread call counter
+		corr = y4_test_light_choice(pix, samp, lc_sub, depth, corr);   // tests/emu only: replays the reference's single-thread call counter
 #endif
 		const int lnum = (int) xmul(y4_halton2_at(sc.base_sampling_offset + corr - 1u, 1u), (float) sc.n_lights);
 		W.lnum[i] = (uint32_t) (lnum < sc.n_lights - 1 ? lnum : sc.n_lights - 1);
@@ -492,13 +497,13 @@ enum : uint32_t { Y4_PUSH_S0 = 1u, Y4_PUSH_S1 = 2u, Y4_PUSH_PATH = 4u, Y4_PUSH_S
 // level > 0: the same for a ray that mirrors reflected (bit 3 of the result: reflected again -> the ray-level queue).
 Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l0, int level)
 {
-	uint32_t f = 0u; Y4Vertex vx;
+	uint32_t f = level > 0 ? W.flags[i] : 0u; Y4Vertex vx;
 	uint32_t push = 0u;
 	const int what = y4_pt_primary(sc, W, i, level, f, vx);
 	if(what == 1)
 	{
 		if(l0 >= 0) push |= y4_pt_direct(sc, W, ps, i, f, true, l0, 0, vx, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
-		if(f & (Y4_PF_DIRECT | Y4_PF_PATHS)) push |= Y4_PUSH_PATH;
+		if(f & (Y4_PF_DIRECT | Y4_PF_PATHS | Y4_PF_RECURSE)) push |= Y4_PUSH_PATH;
 	}
 	else if(what == 2) push |= Y4_PUSH_SPEC;
 	W.flags[i] = f;
@@ -536,7 +541,8 @@ Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 	{
 		const Y4Vertex vx = y4_vertex(sc, y4_level_ray(sc, W, ps, i, f, pix, samp), h);
 		C3 thr = c3f(0.f); Y4Ray out;
-		go = y4_bounce_sample<true>(sc, ps, pix, samp, 0, sub, vx, thr, out);
+		bool specular;
+		go = y4_bounce_sample<true>(sc, ps, pix, samp, 0, sub, vx, thr, out, specular);
 		st3(W.thr, i, thr);
 		if(go) { st_ray(W.ray_next, i, out); f |= Y4_PF_ALIVE; }
 	}
@@ -589,9 +595,10 @@ Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtP
 	if(depth + 1 < sc.bounces)
 	{
 		Y4Ray out;
-		go = y4_bounce_sample<false>(sc, ps, pix, samp, depth + 1, sub, vx, thr, out);
-		// caustic = trace_caustics_ && sampled_flags has Specular | Glossy | Filter (:227): only the mirror samples such a lobe
-		if(go && sc.trace_caustics && (vx.m.bsdf_flags & Y4_BSDF_SPECULAR)) f |= Y4_PF_CAUSTIC; else f &= ~(uint32_t) Y4_PF_CAUSTIC;
+		bool specular;
+		go = y4_bounce_sample<false>(sc, ps, pix, samp, depth + 1, sub, vx, thr, out, specular);
+		// caustic = trace_caustics_ && sampled_flags has Specular | Glossy | Filter (:227)
+		if(go && sc.trace_caustics && specular) f |= Y4_PF_CAUSTIC; else f &= ~(uint32_t) Y4_PF_CAUSTIC;
 		if(go) { st_ray(W.ray_next, i, out); st3(W.thr, i, thr); }
 		else if(f & Y4_PF_DIRECT) st_ray(W.ray_next, i, y4_null_ray());
 	}
@@ -599,6 +606,48 @@ Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtP
 	if(go || (f & Y4_PF_DIRECT)) push |= Y4_PUSH_PATH;
 	W.flags[i] = f;
 	return push;
+}
+
+// radiance integrate() returns at the current ray level, before recursiveRaytrace's share: col + path_col / n_samples
+Y4_HD C3 y4_level_radiance(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t f, float4 col4)
+{
+	C3 col = c3(col4.x, col4.y, col4.z);
+	if(f & Y4_PF_PATHS) col = cadd(col, cdiv(ld3(W.pcol, i), (float) (sc.n_paths > 1 ? sc.n_paths : 1)));
+	return col;
+}
+
+// ---- stage: end of a ray level for vertices with a mirror component (shinydiffusemat specular_reflect) -------------
+// The vertex's own estimate (emission + lights + sub-paths) is complete: fold it into W.acc with the weight of the chain so
+// far, then reflect the level's ray (ShinyDiffuseMaterial::getSpecular, material_shiny_diffuse.cc:400-440; specularReflect,
+// integrator_montecarlo.cc:868-887).  Returns Y4_PUSH_SPEC when the pixel-sample goes on to the next level.
+Y4_HD uint32_t y4_stage_level_finish(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int level)
+{
+	uint32_t f = W.flags[i];
+	if(!(f & Y4_PF_RECURSE)) return 0u;
+	const C3 col = y4_level_radiance(sc, W, i, f, ld4(W.col, i));
+	const float4 sw4 = (f & Y4_PF_SPEC) ? ld4(W.sw, i) : f4(1.f, 1.f, 1.f, 0.f);
+	const C3 sw = c3(sw4.x, sw4.y, sw4.z);
+	C3 acc = (f & Y4_PF_SPEC) ? cmul(col, sw) : col;
+	if(f & Y4_PF_ACC) acc = cadd(ld3(W.acc, i), acc);
+	st3(W.acc, i, acc);
+	const Y4Vertex vx = y4_vertex(sc, y4_level_ray(sc, W, ps, i, f, W.pix[i], W.samp[i]), ld_hit(W.hit0, i));
+	const bool backface = xdot(vx.wo, vx.sp.ng) < 0.f;
+	const V3 n = backface ? xneg(vx.sp.n) : vx.sp.n, ng = backface ? xneg(vx.sp.ng) : vx.sp.ng;
+	const float kr = y4_fresnel_kr(vx.m, vx.wo, n);
+	const float vn = xmul(2.f, xdot(vx.wo, n));                                  // Vec3::reflect (vector.h:227-232)
+	V3 dir = v3(xsub(xmul(vn, n.x), vx.wo.x), xsub(xmul(vn, n.y), vx.wo.y), xsub(xmul(vn, n.z), vx.wo.z));
+	const float cos_wi_ng = xdot(dir, ng);
+	if((double) cos_wi_ng < 0.01)
+	{
+		const float k = (float) (0.01 - (double) cos_wi_ng);
+		dir = xnormalize(v3(xadd(dir.x, xmul(k, ng.x)), xadd(dir.y, xmul(k, ng.y)), xadd(dir.z, xmul(k, ng.z))));
+	}
+	C3 w = cscale(vx.m.mirror_color, xmul(vx.m.mirror_strength, kr));
+	if(f & Y4_PF_SPEC) w = cmul(sw, w);
+	st_ray(W.ray0, i, y4_mk_ray(vx.sp.p, sc.ray_min_dist, dir, -1.f));
+	st4(W.sw, i, f4(w.r, w.g, w.b, y4_u2f((uint32_t) (level + 1))));
+	W.flags[i] = Y4_PF_SPEC | Y4_PF_ACC;
+	return Y4_PUSH_SPEC;
 }
 
 // ---- stage: close the pixel-sample and splat it into the film ----------------------------------------
@@ -613,10 +662,10 @@ Y4_HD void y4_pt_finish_splat(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 {
 	const uint32_t f = W.flags[i];
 	const float4 col4 = ld4(W.col, i);
-	C3 col = c3(col4.x, col4.y, col4.z);
+	C3 col = y4_level_radiance(sc, W, i, f, col4);
 	float alpha = col4.w;
-	if(f & Y4_PF_PATHS) col = cadd(col, cdiv(ld3(W.pcol, i), (float) (sc.n_paths > 1 ? sc.n_paths : 1)));
 	if(f & Y4_PF_SPEC) col = cmul(col, ld3(W.sw, i));               // specularReflect: integ.first *= reflect_data->col_, every level
+	if(f & Y4_PF_ACC) col = cadd(ld3(W.acc, i), col);               // + what the upper levels gathered themselves
 	if(alpha > 1.f) alpha = 1.f;
 	if(sc.clamp_samples > 0.f)      // Rgb::clampProportionalRgb (color.h:415-445)
 	{

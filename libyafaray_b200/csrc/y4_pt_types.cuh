@@ -52,6 +52,9 @@ struct Y4PtMaterial
 	int double_sided, receive_shadows, flat_material;
 	int layer_first, layer_count;   // diffuse_shader chain in Y4PtScene::layers (0 layers: plain colour)
 	float emit_strength;            // emit() with a diffuse_shader: shader colour * emit_strength_
+	// shinydiffusemat's perfect-mirror component (components_[0]): specular_reflect, mirror_color, Fresnel weighting
+	int is_mirror; float mirror_strength; C3 mirror_color;
+	int fresnel; float ior_squared;
 };
 
 // ImageTexture state (texture_image.cc:476-597) + texels as Image::getColor returns them
@@ -101,7 +104,8 @@ struct Y4PtScene
 	// integrator
 	int bounces, n_paths, rr_min_bounces, no_recursive, transp_background;
 	int raydepth, trace_caustics, transp_refracted_background;
-	int has_specular;               // some material needs the ray-level loop (recursiveRaytrace)
+	int has_specular;               // ray-level loop (recursiveRaytrace) needed: 1 pure mirrors only (chains run inside the camera-hit
+	                                // step), 2 shinydiffuse with a mirror component (one full estimate per ray level)
 	C3 background;
 	float shadow_bias; int shadow_bias_auto;
 	float ray_min_dist; int ray_min_dist_auto;
@@ -146,5 +150,8 @@ enum : uint32_t
 	Y4_PF_SPEC = 512u,           // the vertex integrate() works on was reached through mirrors (ray_level > 0): W.ray0 is the ray
 	                             // into it, W.sw the product of the reflection colours (xyz) and the ray level (w)
 	Y4_PF_EMIT1 = 1024u,         // first path vertex's material has Emit (mat_bsd_fs, integrator_path_tracer.cc:196,256)
+	Y4_PF_RECURSE = 4096u,       // the vertex also has a perfect-mirror component and a ray level left: after its own estimate is
+	                             // complete the level-finish stage folds it into W.acc and reflects the ray (shinydiffusemat)
+	Y4_PF_ACC = 8192u,           // W.acc holds the radiance gathered at the upper ray levels of this pixel-sample
 	Y4_PF_CAUSTIC = 2048u        // the ray into the current path vertex was sampled from a specular lobe and caustic_type traces them
 };

@@ -200,11 +200,9 @@ class Interface:
         p = dict(self.params)
         t = p.get("type")
         if t == "shinydiffusemat":
-            for k in ("specular_reflect", "transparency", "translucency"):
+            for k in ("transparency", "translucency"):
                 if float(p.get(k, 0.0)) != 0.0:
                     raise Y4Error(f"shinydiffusemat '{name}': {k} != 0 is not supported by the GPU back end")
-            if p.get("fresnel_effect", False):
-                raise Y4Error(f"shinydiffusemat '{name}': fresnel_effect is not supported by the GPU back end")
             if float(p.get("wireframe_amount", 0.0)) != 0.0:
                 raise Y4Error(f"shinydiffusemat '{name}': wireframe shading is not supported by the GPU back end")
             for k in p:
@@ -519,6 +517,8 @@ class Interface:
                 m.type, m.diffuse_reflect = _lib.MAT_MIRROR, float(p.get("reflect", 1.0))
             else:
                 m.type, m.diffuse_reflect, m.emit = _lib.MAT_SHINYDIFFUSE, float(p.get("diffuse_reflect", 1.0)), float(p.get("emit", 0.0))
+                m.specular_reflect, m.fresnel_effect, m.ior = float(p.get("specular_reflect", 0.0)), int(p.get("fresnel_effect", False)), float(p.get("IOR", 1.33))
+                m.mirror_color[:] = p.get("mirror_color", (1.0, 1.0, 1.0, 1.0))[:3]
                 if p.get("diffuse_brdf", "lambert") == "oren_nayar":
                     m.oren_nayar, m.sigma = 1, float(p.get("sigma", 0.1))
 
@@ -563,8 +563,8 @@ class Interface:
             pr.bounces, pr.path_samples = 1, 0
         pr.russian_roulette_min_bounces, pr.no_recursive = int(integ.get("russian_roulette_min_bounces", 0)), int(integ.get("no_recursive", False))
         pr.transp_background = int(integ.get("bg_transp", False))
-        if pr.no_recursive and any(self.materials[n]["type"] == "mirror" for n in mat_names):
-            raise Y4Error("no_recursive with mirror materials is not supported by the GPU back end")
+        if pr.no_recursive and any(self.materials[n]["type"] == "mirror" or float(self.materials[n].get("specular_reflect", 0.0)) > 0.00001 for n in mat_names):
+            raise Y4Error("no_recursive with mirror materials / specular_reflect is not supported by the GPU back end")
         pr.raydepth, pr.transp_refracted_background = int(integ.get("raydepth", 5)), int(integ.get("bg_transp_refract", False))
         pr.trace_caustics = int(integ.get("type") == "pathtracing" and integ.get("caustic_type", "path") not in ("none", "photon"))
         pr.transp_shadows, pr.shadow_depth = int(bool(integ.get("transpShad", False))), int(integ.get("shadowDepth", 4))

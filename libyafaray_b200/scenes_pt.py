@@ -19,6 +19,8 @@ def _material(api, name, color, diffuse_reflect=1.0, **extra):
             api.paramsSetString(k, v)
         elif isinstance(v, bool):
             api.paramsSetBool(k, v)
+        elif isinstance(v, (tuple, list)):
+            api.paramsSetColor(k, float(v[0]), float(v[1]), float(v[2]), 1.0)
         else:
             api.paramsSetFloat(k, float(v))
     api.createMaterial(name)
@@ -82,13 +84,14 @@ def _uv_sphere(centre, radius, nu, nv):
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
                 oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None,
-                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0):
+                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front.
     mirror: {"objects": subset of ("tall", "short", "back", "left", "sphere"), "color": rgb, "reflect": r} -> those objects get a
     `mirror` material; integrator_extra: integrator parameters set after the defaults (raydepth, caustic_type, ...)."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
+    extra.update(shiny or {})          # shiny: shinydiffusemat parameters of all three wall materials (specular_reflect, mirror_color, fresnel_effect, IOR)
     _material(api, "white", white, **extra)
     _material(api, "red", red, **extra)
     _material(api, "green", green, **({**extra, "emit": glow} if glow else extra))       # glow: the right wall also emits

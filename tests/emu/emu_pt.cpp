@@ -12,7 +12,7 @@
 // the emulation can replay (mode 1 records which vertices ask, emu_light_choice_finalize numbers them in the reference's
 // tile / pixel / sample / sub-path / depth order, mode 2 feeds the numbers back).  The product keeps its per-vertex index.
 #define Y4_TEST_LIGHT_CHOICE_HOOK 1
-typedef std::tuple<uint32_t, uint32_t, int, int> LcKey;      // pixel, sample, sub-path, depth
+typedef std::tuple<uint32_t, uint32_t, int, int> LcKey;      // pixel, sample, ray level * 4096 + sub-path, depth
 static int g_lc_mode = 0;
 static std::map<LcKey, uint32_t> g_lc;
 static void y4_test_light_choice_called(uint32_t pix, uint32_t samp, int sub, int depth) { if(g_lc_mode == 1) g_lc[LcKey(pix, samp, sub, depth)] = 0u; }
@@ -107,7 +107,11 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	sc.no_recursive = params->no_recursive; sc.transp_background = params->transp_background;
 	sc.raydepth = params->raydepth; sc.trace_caustics = params->trace_caustics; sc.transp_refracted_background = params->transp_refracted_background;
 	sc.has_specular = 0;
-	for(uint32_t m = 0; m < n_mat; ++m) if(mats[m].type == Y4GPU_MAT_MIRROR) sc.has_specular = 1;
+	for(uint32_t m = 0; m < n_mat; ++m)
+	{
+		if(mats[m].type == Y4GPU_MAT_MIRROR && !sc.has_specular) sc.has_specular = 1;
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].specular_reflect > 0.00001f) sc.has_specular = 2;
+	}
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
@@ -136,13 +140,13 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	std::vector<uint32_t> pix(n), samp(n), fl(n), lnum(n);
 	std::vector<float4> col(n), pcol(n), thr(n), pthr(n), lcol(n), acc_a(n), acc_b(n), lsamp(n), scontrib(2ull * n);
 	std::vector<Y4Ray> ray(n), ray2(n), sray(2ull * n), ray0(n);
-	std::vector<float4> sw(n);
+	std::vector<float4> sw(n), acc(n);
 	std::vector<Y4Hit> hit(n), hit0(n), shit(2ull * n);
 	Y4PtWave W;
 	W.n = n; W.pix = pix.data(); W.samp = samp.data(); W.flags = fl.data(); W.lnum = lnum.data();
 	W.col = &col[0].x; W.pcol = &pcol[0].x; W.thr = &thr[0].x; W.lcol = &lcol[0].x; W.acc_a = &acc_a[0].x; W.acc_b = &acc_b[0].x; W.lsamp = &lsamp[0].x; W.pthr = &pthr[0].x;
 	W.ray = ray.data(); W.ray_next = ray2.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = &scontrib[0].x;
-	W.ray0 = ray0.data(); W.sw = &sw[0].x;
+	W.ray0 = ray0.data(); W.sw = &sw[0].x; W.acc = &acc[0].x;
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
 	for(uint32_t i = 0; i < n; ++i) { pix[i] = pixel_list ? pixel_list[i / ns_local] : i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
 	const int shadow_kind = params->transp_shadows ? Y4_TRACE_TSHADOW : Y4_TRACE_SHADOW;
@@ -161,12 +165,25 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		push(p, i, n, &q_hit0, &q_shadow);
 		if(p & Y4_PUSH_SPEC) q_spec_next.push_back(i);
 	};
-	for(uint32_t i = 0; i < n; ++i) primary(i, 0);
-	for(int level = 1; sc.has_specular && level <= sc.raydepth && level < 20; ++level)      // ray levels, as y4gpu_pt_render_pass
+	// ray levels, as y4gpu_pt_render_pass: whole mirror chains inside the camera-hit step when only pure mirrors exist,
+	// one estimate per level when shinydiffuse materials have a mirror component
+	const int max_level = (sc.has_specular && sc.raydepth > 0) ? (sc.raydepth < 19 ? sc.raydepth : 19) : 0;
+	const bool level_runs = sc.has_specular == 2;
+	for(int level = 0; level <= (level_runs ? max_level : 0); ++level)
+	{
+	q_hit0.clear(); q_shadow.clear();
+	if(level == 0) for(uint32_t i = 0; i < n; ++i) primary(i, 0);
+	else
 	{
 		q_spec.swap(q_spec_next); q_spec_next.clear();
 		trace(bvh, Y4_TRACE_CLOSEST, W.ray0, q_spec.data(), q_spec.size(), W.hit);
 		for(uint32_t i : q_spec) primary(i, level);
+	}
+	for(int lv = 1; !level_runs && lv <= max_level; ++lv)
+	{
+		q_spec.swap(q_spec_next); q_spec_next.clear();
+		trace(bvh, Y4_TRACE_CLOSEST, W.ray0, q_spec.data(), q_spec.size(), W.hit);
+		for(uint32_t i : q_spec) primary(i, lv);
 	}
 	for(size_t j = 0; j < all_lk.size(); ++j)
 	{
@@ -207,6 +224,9 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		}
 	}
 	W.ray = ray_buf[0];
+	if(level_runs && level < max_level)
+		for(uint32_t i : q_hit0) if(y4_stage_level_finish(sc, W, ps, i, level) & Y4_PUSH_SPEC) q_spec_next.push_back(i);
+	}   // ray levels
 	for(uint32_t i = 0; i < n; ++i) y4_pt_finish_splat(sc, W, ps, i, film_w, film_rgba);
 	return 0;
 }

@@ -79,6 +79,12 @@ PT_GOLDEN_MIRROR = {
                                       integrator_extra=dict(raydepth=2, caustic_type="path")),
     "mirror_hall_raydepth8": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, point_light=True, filter_type="gauss",
                                   mirror=dict(objects=("tall", "back", "left", "short")), integrator_extra=dict(raydepth=8, caustic_type="path")),
+    # shinydiffusemat with a mirror component (specular_reflect, mirror_color, Fresnel): one estimate per ray level
+    "shiny_walls_raydepth3": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, shiny=dict(specular_reflect=0.3, mirror_color=(0.9, 0.7, 0.5)),
+                                  integrator_extra=dict(raydepth=3, caustic_type="path")),
+    "shiny_fresnel_mirror_box_glow": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, shiny=dict(specular_reflect=0.6, fresnel_effect=True, IOR=1.8),
+                                          mirror=dict(objects=("tall",), color=(0.9, 0.95, 0.8)), glow=0.5, oren_nayar=True, path_samples=2, light_samples=2,
+                                          integrator_extra=dict(raydepth=2, caustic_type="path")),
     "mirror_sphere_transp_bg_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", smooth_sphere=180.0,
                                            mirror=dict(objects=("sphere", "short")), background=(0.3, 0.2, 0.1),
                                            integrator_extra=dict(raydepth=2, bg_transp=True, bg_transp_refract=True)),

@@ -282,6 +282,30 @@ def test_mirror_material_vs_live_reference(variant):
     assert np.abs(img[..., 3] - ref[..., 3]).max() <= 1e-6
 
 
+SHINY = [dict(shiny=dict(specular_reflect=0.3), integrator_extra=dict(raydepth=0)),                                            # component sampled in paths, no recursion
+         dict(shiny=dict(specular_reflect=0.3), integrator_extra=dict(raydepth=1)),
+         dict(shiny=dict(specular_reflect=0.4), mirror=dict(objects=("tall",)), integrator="directlighting", background=(0.3, 0.2, 0.1),
+              integrator_extra=dict(raydepth=4, bg_transp=True)),
+         dict(shiny=dict(specular_reflect=0.5, fresnel_effect=True), extra_lights=("sphere", "spot"), integrator_extra=dict(raydepth=2, caustic_type="path"))]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("variant", SHINY)
+def test_shinydiffuse_mirror_component_vs_live_reference(variant):
+    """shinydiffusemat specular_reflect / mirror_color / fresnel_effect / IOR: ShinyDiffuseMaterial::config, accumulate,
+    getFresnelKr, the two-component sample / eval / pdf, getSpecular (grazing-angle fix) and the ray-level recursion in which
+    every level adds its own estimate (emission + lights + sub-paths) before the reflected ray is followed."""
+    kw = dict(width=64, height=36, spp=3, bounces=4, **variant)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    a = _assemble(**kw)
+    w, rgba = helpers.emu_pt_render(a, ref_light_order=a["n_light"] > 1 and a["params"].path_samples > 0)
+    img = interface.normalize_film(w, rgba)
+    assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
+    assert np.abs(img[..., 3] - ref[..., 3]).max() <= 1e-6
+
+
 def test_mirror_with_no_recursive_is_rejected():
     """no_recursive makes a mirror hit both start sub-paths and recurse (two branches per vertex): not covered, so refused."""
     yi = interface.Interface()
