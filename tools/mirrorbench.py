@@ -18,12 +18,12 @@ def main():
                               integrator_extra=dict(raydepth=5, caustic_type="path"), **kw)
         yi.upload()
         for r in range(reps):
-            st = {"scene": name, "samples": 0, "rays_closest": 0, "rays_shadow": 0, "kernel_launches": 0, "pass_ms": 0.0}
+            st = {"samples": 0, "rays_closest": 0, "rays_shadow": 0, "kernel_launches": 0, "pass_ms": 0.0}
             yi.render_pass(spp, r * spp, 0)
             yi._add_stats(st)
             st["msamples_s"] = st["samples"] / st["pass_ms"] * 1e-3
             st["mrays_s"] = (st["rays_closest"] + st["rays_shadow"]) / st["pass_ms"] * 1e-3
-            print(json.dumps(st), flush=True)
+            print(json.dumps({"scene": name, **st}), flush=True)
         yi.clearAll()
 
 
