@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_gen(const __grid_constant__ Y
 	}
 }
 
-template<int STAGE, int MINB>
+template<int STAGE, int MINB, bool SPEC>
 __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, StageArgs a, StageQueues Q)
 {
 	const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
@@ -113,11 +113,11 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 		if(q < count)
 		{
 			i = Q.in_q ? Q.in_q[q] : q;
-			if(STAGE == kStPrimary) push = y4_stage_primary(sc, W, ps, i, a.l, a.level);
-			else if(STAGE == kStDirectStep) push = y4_stage_direct_step(sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
-			else if(STAGE == kStStart) push = y4_stage_start(sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
+			if(STAGE == kStPrimary) push = y4_stage_primary<SPEC>(sc, W, ps, i, a.l, a.level);
+			else if(STAGE == kStDirectStep) push = y4_stage_direct_step<SPEC>(sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
+			else if(STAGE == kStStart) push = y4_stage_start<SPEC>(sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
 			else if(STAGE == kStLevelFinish) push = y4_stage_level_finish(sc, W, ps, i, a.level);
-			else push = y4_stage_path(sc, W, ps, i, a.depth, a.sub, a.k_prev);
+			else push = y4_stage_path<SPEC>(sc, W, ps, i, a.depth, a.sub, a.k_prev);
 		}
 		// queue appends: one atomic per warp; when a stage feeds both queues their two 32-bit lengths share one 64-bit
 		// counter slot (path count low, shadow count high) and a single 64-bit atomic reserves both ranges
@@ -187,9 +187,20 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_splat(const __grid_constant__
 template<int STAGE>
 void launch_stage(int minb, int grid, cudaStream_t st, const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, const StageArgs &a, const StageQueues &Q)
 {
-	if(minb >= 4) k_pt_stage<STAGE, 4><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
-	else if(minb == 3) k_pt_stage<STAGE, 3><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
-	else k_pt_stage<STAGE, 2><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+	// second instantiation for scenes without specular materials: see y4_vertex
+	if(sc.has_specular || STAGE == kStLevelFinish)
+	{
+		if(minb >= 4) k_pt_stage<STAGE, 4, true><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+		else if(minb == 3) k_pt_stage<STAGE, 3, true><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+		else k_pt_stage<STAGE, 2, true><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+	}
+	else
+	{
+		constexpr int S = STAGE == kStLevelFinish ? kStPath : STAGE;      // (never launched without specular materials)
+		if(minb >= 4) k_pt_stage<S, 4, false><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+		else if(minb == 3) k_pt_stage<S, 3, false><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+		else k_pt_stage<S, 2, false><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
+	}
 }
 
 inline int pt_grid(const y4gpu_ctx *ctx, uint32_t n)

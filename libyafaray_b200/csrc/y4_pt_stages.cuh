@@ -217,12 +217,17 @@ Y4_HD void y4_pt_gen(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps,
 }
 
 struct Y4Vertex { Y4Surf sp; Y4PtMaterial m; V3 wo; };
+// SPEC = false: the scene has no material with a specular component (Y4PtScene::has_specular == 0).  The kernels are
+// compiled a second time for that case with the mirror fields of the material copy forced to constants, so that the
+// reflection code folds away and costs plain diffuse scenes no registers (the emulation and specular scenes use SPEC = true).
+template<bool SPEC = true>
 Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 {
 	Y4Vertex v;
 	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
 	v.sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
 	v.m = sc.mats[v.sp.mat];
+	if(!SPEC) { v.m.is_mirror = 0; v.m.fresnel = 0; if(v.m.type == Y4GPU_MAT_MIRROR) v.m.type = Y4GPU_MAT_SHINYDIFFUSE; }
 	if(v.m.layer_count > 0)          // initBsdf evaluates the node chain; getShaderColor / emit() read it (material_shiny_diffuse.cc:237,244)
 	{
 		v.m.color = y4_diffuse_shader_color(sc, v.m, v.sp, h.bu, h.bv, h.prim);
@@ -238,6 +243,7 @@ Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 // reflected ray was written to W.ray0 (recursiveRaytrace -> specularReflect -> integrate at level + 1,
 // integrator_montecarlo.cc:868-964; the chain's colour factors are multiplied up front into W.sw and applied when the
 // pixel-sample is splatted: same factors as the reference's unwinding products, in the opposite order).
+template<bool SPEC = true>
 Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int level, uint32_t &f, Y4Vertex &vx)
 {
 	const Y4Hit h = ld_hit(W.hit, i);
@@ -252,9 +258,9 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 		return 0;
 	}
 	st_hit(W.hit0, i, h);
-	vx = y4_vertex(sc, r, h);
-	const bool deeper = level + 1 <= sc.raydepth && level + 1 < 20;
-	if(vx.m.type == Y4GPU_MAT_MIRROR && deeper)
+	vx = y4_vertex<SPEC>(sc, r, h);
+	const bool deeper = SPEC && level + 1 <= sc.raydepth && level + 1 < 20;
+	if(SPEC && vx.m.type == Y4GPU_MAT_MIRROR && deeper)
 	{
 		// MirrorMaterial::getSpecular (material_glass.cc:443-451) + specularReflect
 		const V3 dir = y4_reflect_dir(y4_face_forward(vx.sp.ng, vx.sp.n, vx.wo), vx.wo);
@@ -280,9 +286,10 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 
 // the ray integrate() was called with for this pixel-sample: the camera ray (recomputed, cheaper than a 32-byte read) or the
 // stored reflected ray
+template<bool SPEC = true>
 Y4_HD Y4Ray y4_level_ray(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t f, uint32_t pix, uint32_t samp)
 {
-	return (f & Y4_PF_SPEC) ? ld_ray(W.ray0, i) : y4_primary_ray(sc, ps, pix, samp);
+	return (SPEC && (f & Y4_PF_SPEC)) ? ld_ray(W.ray0, i) : y4_primary_ray(sc, ps, pix, samp);
 }
 
 // number of samples doLightEstimation takes from light L (integrator_montecarlo.cc:396)
@@ -495,11 +502,12 @@ enum : uint32_t { Y4_PUSH_S0 = 1u, Y4_PUSH_S1 = 2u, Y4_PUSH_PATH = 4u, Y4_PUSH_S
 // camera-ray hit + first direct-light sample (light l0, k = 0; l0 < 0: scene without lights).
 // Output queue: paths that hit a surface and have more to do (more light samples or sub-paths).
 // level > 0: the same for a ray that mirrors reflected (bit 3 of the result: reflected again -> the ray-level queue).
+template<bool SPEC = true>
 Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l0, int level)
 {
 	uint32_t f = level > 0 ? W.flags[i] : 0u; Y4Vertex vx;
 	uint32_t push = 0u;
-	const int what = y4_pt_primary(sc, W, i, level, f, vx);
+	const int what = y4_pt_primary<SPEC>(sc, W, i, level, f, vx);
 	if(what == 1)
 	{
 		if(l0 >= 0) push |= y4_pt_direct(sc, W, ps, i, f, true, l0, 0, vx, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
@@ -511,6 +519,7 @@ Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4
 }
 
 // resolve sample (l_prev, k_prev), take sample (l, k); camera-hit vertex (all_lights) or current path vertex
+template<bool SPEC = true>
 Y4_HD uint32_t y4_stage_direct_step(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, bool all_lights, int l_prev, int k_prev, int l, int k)
 {
 	uint32_t f = W.flags[i];
@@ -520,8 +529,8 @@ Y4_HD uint32_t y4_stage_direct_step(const Y4PtScene &sc, const Y4PtWave &W, cons
 	int ll, ns;
 	if(y4_direct_active(sc, W, i, f, all_lights, l, k, ll, ns))
 	{
-		const Y4Ray r = all_lights ? y4_level_ray(sc, W, ps, i, f, W.pix[i], W.samp[i]) : ld_ray(W.ray, i);
-		const Y4Vertex vx = y4_vertex(sc, r, all_lights ? ld_hit(W.hit0, i) : ld_hit(W.hit, i));
+		const Y4Ray r = all_lights ? y4_level_ray<SPEC>(sc, W, ps, i, f, W.pix[i], W.samp[i]) : ld_ray(W.ray, i);
+		const Y4Vertex vx = y4_vertex<SPEC>(sc, r, all_lights ? ld_hit(W.hit0, i) : ld_hit(W.hit, i));
 		push = y4_pt_direct(sc, W, ps, i, f, all_lights, l, k, vx, cache);
 	}
 	W.flags[i] = f;
@@ -529,6 +538,7 @@ Y4_HD uint32_t y4_stage_direct_step(const Y4PtScene &sc, const Y4PtWave &W, cons
 }
 
 // start sub-path `sub` at the camera hit: [resolve the last all-lights sample] + BSDF sample of bounce 0 -> W.ray_next
+template<bool SPEC = true>
 Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l_last, int k_last, int sub)
 {
 	uint32_t f = W.flags[i];
@@ -539,7 +549,7 @@ Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 	bool go = false;
 	if(f & Y4_PF_PATHS)
 	{
-		const Y4Vertex vx = y4_vertex(sc, y4_level_ray(sc, W, ps, i, f, pix, samp), h);
+		const Y4Vertex vx = y4_vertex<SPEC>(sc, y4_level_ray<SPEC>(sc, W, ps, i, f, pix, samp), h);
 		C3 thr = c3f(0.f); Y4Ray out;
 		bool specular;
 		go = y4_bounce_sample<true>(sc, ps, pix, samp, 0, sub, vx, thr, out, specular);
@@ -556,6 +566,7 @@ Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 //   3. BSDF sample -> the next ray in W.ray_next.
 // A path stays on the output queue while it has a ray to trace OR an estimate waiting to be folded in (such a
 // finished path gets an empty ray).  depth == sc.bounces is the closing call: step 1 only.
+template<bool SPEC = true>
 Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub, int k_last)
 {
 	uint32_t f = W.flags[i];
@@ -573,7 +584,7 @@ Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtP
 	uint32_t push = 0u;
 	if(closing || !(f & Y4_PF_ALIVE)) { f &= ~(uint32_t) Y4_PF_ALIVE; W.flags[i] = f; return 0u; }
 	if(h.prim < 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return 0u; }     // hit background: continue / break
-	const Y4Vertex vx = y4_vertex(sc, r, h);
+	const Y4Vertex vx = y4_vertex<SPEC>(sc, r, h);
 	C3 thr = c3(thr4.x, thr4.y, thr4.z), emit;
 	const int what = y4_bounce_hit(sc, W, ps, i, pix, samp, f, depth, sub, vx, thr, emit);
 	if(what == 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return 0u; }
