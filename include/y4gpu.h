@@ -329,6 +329,9 @@ int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, int aa_pass_
 int y4gpu_pt_next_pass(y4gpu_ctx *ctx, const y4gpu_pt_aa_noise *aa, const float *d_weights, const float *d_rgba,
                        const uint32_t **d_pixel_list, uint64_t *n_resample);
 int y4gpu_pt_read_film(y4gpu_ctx *ctx, float *weights, float *rgba);
+/* Replaces the accumulated film (weights [h*w], rgba [h*w*4]; host or device memory): what ImageFilm::imageFilmLoad /
+ * imageFilmLoadAllInFolder leave in weights_ and the Combined layer before a resumed render (imagefilm.cc:827-1018). */
+int y4gpu_pt_write_film(y4gpu_ctx *ctx, const float *weights, const float *rgba);
 int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out);
 
 #ifdef __cplusplus

@@ -128,7 +128,7 @@ EXPORTED = [
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow",
     "y4gpu_get_stats", "y4gpu_synchronize",
     "y4gpu_pt_set_textures", "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
-    "y4gpu_pt_read_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass",
+    "y4gpu_pt_read_film", "y4gpu_pt_write_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass",
 ]  # fmt: skip
 
 
@@ -185,6 +185,8 @@ def lib() -> C.CDLL:
     L.y4gpu_pt_next_pass.restype = i32
     L.y4gpu_pt_read_film.argtypes = [vp, vp, vp]
     L.y4gpu_pt_read_film.restype = i32
+    L.y4gpu_pt_write_film.argtypes = [vp, vp, vp]
+    L.y4gpu_pt_write_film.restype = i32
     L.y4gpu_pt_get_stats.argtypes = [vp, C.POINTER(PtStats)]
     L.y4gpu_pt_get_stats.restype = i32
     _lib = L

@@ -495,6 +495,20 @@ int y4gpu_pt_read_film(y4gpu_ctx *ctx, float *weights, float *rgba)
 	return Y4GPU_OK;
 }
 
+int y4gpu_pt_write_film(y4gpu_ctx *ctx, const float *weights, const float *rgba)
+{
+	if(!ctx || !weights || !rgba) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4Pt *pt = ctx->pt;
+	if(!pt || !pt->scene_set) { ctx->err = "y4gpu_pt_write_film before y4gpu_pt_set_scene"; return Y4GPU_ERR_ARG; }
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	const size_t npx = (size_t) pt->h_scene.width * pt->h_scene.height;
+	Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_film_w, weights, npx * sizeof(float), cudaMemcpyDefault, ctx->stream));
+	Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_film_rgba, rgba, npx * 4 * sizeof(float), cudaMemcpyDefault, ctx->stream));
+	Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return Y4GPU_OK;
+}
+
 int y4gpu_pt_next_pass(y4gpu_ctx *ctx, const y4gpu_pt_aa_noise *aa, const float *d_weights, const float *d_rgba,
                        const uint32_t **d_pixel_list, uint64_t *n_resample)
 {

@@ -19,7 +19,7 @@ from typing import Dict, List, Optional
 
 import numpy as np
 
-from . import _lib, images
+from . import _lib, film_io, images
 from ._lib import Y4Error
 from .accelerator import ACCELERATOR_TYPE, AcceleratorB200
 
@@ -203,6 +203,8 @@ class Interface:
             for k in ("transparency", "translucency"):
                 if float(p.get(k, 0.0)) != 0.0:
                     raise Y4Error(f"shinydiffusemat '{name}': {k} != 0 is not supported by the GPU back end")
+            if float(p.get("samplingfactor", 1.0)) != 1.0 or int(p.get("additionaldepth", 0)) != 0:
+                raise Y4Error(f"shinydiffusemat '{name}': samplingfactor / additionaldepth are not supported by the GPU back end")
             if float(p.get("wireframe_amount", 0.0)) != 0.0:
                 raise Y4Error(f"shinydiffusemat '{name}': wireframe shading is not supported by the GPU back end")
             for k in p:
@@ -571,6 +573,8 @@ class Interface:
         if bg is not None:
             c, pw = bg.get("color", (0.0, 0.0, 0.0, 1.0)), np.float32(bg.get("power", 1.0))
             pr.background[:] = [float(np.float32(c[k]) * pw) for k in range(3)]
+        if not rp.get("background_resampling", True):
+            raise Y4Error("background_resampling=false is not supported by the GPU back end")
         pr.width, pr.height = int(rp.get("width", cam.resx)), int(rp.get("height", cam.resy))
         pr.xstart, pr.ystart = int(rp.get("xstart", 0)), int(rp.get("ystart", 0))
         pr.aa_passes, pr.aa_samples, pr.aa_inc_samples = int(rp.get("AA_passes", 1)), int(rp.get("AA_minsamples", 1)), int(rp.get("AA_inc_samples", 1))
@@ -583,7 +587,9 @@ class Interface:
         pr.shadow_bias = GLOBAL_SHADOW_BIAS if pr.shadow_bias_auto else float(rp.get("adv_shadow_bias_value", GLOBAL_SHADOW_BIAS))
         pr.min_raydist_auto = int(rp.get("adv_auto_min_raydist_enabled", True))
         pr.min_raydist = GLOBAL_MIN_RAYDIST if pr.min_raydist_auto else float(rp.get("adv_min_raydist_value", GLOBAL_MIN_RAYDIST))
-        pr.base_sampling_offset = (int(rp.get("adv_base_sampling_offset", 0)) + 100000 * int(rp.get("adv_computer_node", 0))) & 0xFFFFFFFF
+        base_offs = getattr(self, "_base_offset_override", None)      # raised by the film files a load-save render starts from
+        base_offs = int(rp.get("adv_base_sampling_offset", 0)) if base_offs is None else base_offs
+        pr.base_sampling_offset = (base_offs + 100000 * int(rp.get("adv_computer_node", 0))) & 0xFFFFFFFF
         pr.rr_seed = int(rp.get("b200_rr_seed", 0x5EED)) & 0xFFFFFFFF
         pr.wave_size = int(rp.get("b200_wave_size", 0))
         pr.profile = int(rp.get("b200_profile", 0))
@@ -655,14 +661,31 @@ class Interface:
         are adaptive: ImageFilm::nextPass flags the noisy pixels (on the device), only those are resampled, and the
         threshold is lowered when fewer than AA_resampled_floor % of the pixels were flagged -- the reference's loop,
         including its fp32 arithmetic.  Returns the normalised Combined layer."""
+        rp = self.render_params
+        # film_load_save_mode (imagefilm.cc:74-118,236-241): "load-save" starts from the sum of the film files in the output
+        # folder and skips pass 0 (integrator_tiled.cc:155-177); "save" / "load-save" write the film file at the end
+        mode, film_file = str(rp.get("film_load_save_mode", "none")), str(rp.get("film_load_save_path", ""))
+        node, own_base = int(rp.get("adv_computer_node", 0)), int(rp.get("adv_base_sampling_offset", 0))
+        self._base_offset_override, resumed = None, None
+        if mode == "load-save":
+            p0 = self.assemble()["params"]
+            lw, lc, base, offs, n_loaded = film_io.load_all_in_folder(film_file, p0.width, p0.height, p0.xstart, p0.ystart, own_base)
+            if n_loaded:
+                resumed, self._base_offset_override = (lw, lc, offs), base
         a = self.upload()
-        pr, rp = a["params"], self.render_params
+        pr = a["params"]
         f32 = np.float32
         L, ctx = self.accelerator._L, self.accelerator.ctx
         _lib.check(ctx, L.y4gpu_pt_clear_film(ctx), "y4gpu_pt_clear_film")
         stats = {"samples": 0, "rays_closest": 0, "rays_shadow": 0, "kernel_launches": 0, "pass_ms": 0.0}
-        self.render_pass(pr.aa_samples, 0, 0)
-        self._add_stats(stats)
+        self.resumed = resumed is not None
+        if resumed is not None:                                 # renderPass(0, film sampling offset): nothing is rendered
+            _lib.check(ctx, L.y4gpu_pt_write_film(ctx, C.c_void_p(resumed[0].ctypes.data), C.c_void_p(resumed[1].ctypes.data)), "y4gpu_pt_write_film")
+            self.sampling_offset = resumed[2]
+        else:
+            self.render_pass(pr.aa_samples, 0, 0)
+            self._add_stats(stats)
+            self.sampling_offset = pr.aa_samples
         threshold = f32(rp.get("AA_threshold", 0.05))
         floor_pixels = int(np.floor(f32(f32(rp.get("AA_resampled_floor", 0.0)) * f32(pr.width * pr.height)) / f32(100.0)))
         acum, mult = pr.aa_samples, f32(1.0)
@@ -684,6 +707,7 @@ class Interface:
             if not skip and resampled > 0:
                 self.render_pass(n, acum, i, pixel_list=plist)
                 self._add_stats(stats)
+                self.sampling_offset = acum + n                # ImageFilm::setSamplingOffset(offset + samples)
             acum += n
             if resampled < floor_pixels:
                 ratio = min(f32(8.0), f32(floor_pixels) / f32(resampled)) if resampled > 0 else f32(8.0)
@@ -691,6 +715,10 @@ class Interface:
                 if threshold > 0:
                     threshold_changed = True
         self.last_stats = stats
+        if mode in ("save", "load-save"):                       # ImageFilm::flush -> imageFilmSave
+            fw, frgba = self.read_film()
+            film_io.save_film(film_io.film_path(film_file, node), fw, frgba, node, own_base if self._base_offset_override is None else self._base_offset_override,
+                              self.sampling_offset, pr.xstart, pr.ystart)
         return self.read_image()
 
     def pass_stats(self) -> dict:

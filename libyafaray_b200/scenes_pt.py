@@ -84,7 +84,7 @@ def _uv_sphere(centre, radius, nu, nv):
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
                 oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None,
-                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None):
+                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front.
     mirror: {"objects": subset of ("tall", "short", "back", "left", "sphere"), "color": rgb, "reflect": r} -> those objects get a
@@ -247,6 +247,7 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     api.paramsSetString("filter_type", filter_type)
     api.paramsSetString("tiles_order", "linear")
     api.paramsSetInt("tile_size", 32)
+    _set_params(api, render_extra)      # e.g. AA_passes, film_load_save_mode / film_load_save_path, adv_computer_node
     api.setupRender()
 
 

@@ -189,3 +189,26 @@ def test_full_size_c2_film_properties():
         ws, cs = ws + w, cs + c
     assert np.array_equal(w1, ws) and np.allclose(c1, cs, rtol=1e-5, atol=1e-5)
     assert one.last_stats["samples"] == 1920 * 1080 * 2 and one.last_stats["rays_closest"] > one.last_stats["samples"]
+
+
+def test_film_save_and_load_save_resume(tmp_path):
+    """film_load_save_mode through Interface.render(): "save" writes the reference's film file; "load-save" starts from the
+    films in the folder, skips pass 0 (nothing is rendered with AA_passes=1) and continues with the later passes."""
+    from libyafaray_b200 import film_io
+
+    path = str(tmp_path / "cornell.tga")
+    kw = dict(width=64, height=36, spp=2, bounces=2)
+    one = _gpu(render_extra=dict(film_load_save_mode="save", film_load_save_path=path), **kw)
+    img1 = one.render()
+    w1, c1 = one.read_film()
+    f = film_io.load_film(film_io.film_path(path, 0), 64, 36)
+    assert f["sampling_offset"] == 2 and np.array_equal(f["weights"], w1) and np.array_equal(f["layers"][0], c1)
+    two = _gpu(render_extra=dict(film_load_save_mode="load-save", film_load_save_path=path), **kw)
+    img2 = two.render()
+    assert two.resumed and two.last_stats["samples"] == 0 and np.array_equal(img1, img2)
+    more = _gpu(render_extra=dict(film_load_save_mode="load-save", film_load_save_path=path, AA_passes=2, AA_inc_samples=3, AA_threshold=0.0), **kw)
+    more.render()
+    w3, c3 = more.read_film()
+    assert more.resumed and more.last_stats["samples"] == 64 * 36 * 3
+    assert (w3 >= w1).all() and abs(float(w3.sum()) / float(w1.sum()) - 2.5) < 0.05 and np.isfinite(c3).all()
+    assert film_io.load_film(film_io.film_path(path, 0), 64, 36)["sampling_offset"] == 5
