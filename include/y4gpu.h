@@ -155,7 +155,8 @@ typedef struct y4gpu_pt_material
 	float mirror_color[3];        /* shinydiffusemat `mirror_color` (default 1 1 1) */
 	int32_t fresnel_effect;       /* shinydiffusemat `fresnel_effect`: the mirror component is weighted by the Fresnel term of `ior` */
 	float ior;                    /* shinydiffusemat `IOR` (default 1.33) */
-	int32_t reserved[2];
+	float transparency;           /* shinydiffusemat `transparency` (default 0): light passes straight through, tinted by the filter */
+	float transmit_filter;        /* shinydiffusemat `transmit_filter` (default 1): share of the diffuse colour in that tint */
 } y4gpu_pt_material;
 
 /* Image textures and the `diffuse_shader` node chains of shinydiffusemat: texture_mapper + layer nodes

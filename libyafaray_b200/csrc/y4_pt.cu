@@ -374,8 +374,15 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	for(uint32_t m = 0; m < n_mat; ++m)
 	{
 		if(mats[m].type == Y4GPU_MAT_MIRROR && !sc.has_specular) sc.has_specular = 1;
-		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].specular_reflect > 0.00001f) sc.has_specular = 2;
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f)) sc.has_specular = 2;
 	}
+	for(uint32_t m = 0; m < n_mat; ++m)
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].transparency > 0.00001f)
+		{
+			// reflect + refract at one vertex = two child rays (a tree, not a chain); filtered shadows need the blockers' colours
+			if(mats[m].specular_reflect > 0.00001f) { ctx->err = "shinydiffusemat with both specular_reflect and transparency is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
+			if(params->transp_shadows) { ctx->err = "transparent materials with transpShad are not supported"; return Y4GPU_ERR_UNSUPPORTED; }
+		}
 	// no_recursive makes a mirror hit start sub-paths AND recurse: two branches per vertex, which the linear ray-level chain does not cover
 	if(sc.has_specular && sc.no_recursive) { ctx->err = "no_recursive with mirror materials / specular_reflect is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);

@@ -103,7 +103,7 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 	o.layer_first = m.layer_first; o.layer_count = m.layer_count; o.emit_strength = m.emit;
 	o.emit = c3(m.emit * m.color[0], m.emit * m.color[1], m.emit * m.color[2]);
 	if(m.emit > 0.f) o.bsdf_flags |= Y4_BSDF_EMIT;
-	float acc = 1.f;                                          // config() (:39-82); no transparency / translucency components
+	float acc = 1.f;                                          // config() (:39-82); no translucency component
 	o.mirror_color = c3(m.mirror_color[0], m.mirror_color[1], m.mirror_color[2]);
 	if(m.specular_reflect > 0.00001f)
 	{
@@ -112,6 +112,13 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 		o.bsdf_flags |= Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT;
 	}
 	if(m.fresnel_effect) { o.fresnel = 1; o.ior_squared = m.ior * m.ior; }
+	o.transmit_filter = m.transmit_filter;
+	if(m.transparency * acc > 0.00001f)
+	{
+		o.is_transparent = 1; o.transparency_strength = m.transparency;
+		acc *= 1.f - m.transparency;
+		o.bsdf_flags |= Y4_BSDF_TRANSMIT | Y4_BSDF_FILTER;
+	}
 	if(m.diffuse_reflect * acc > 0.00001f)
 	{
 		o.is_diffuse = 1; o.diffuse_strength = m.diffuse_reflect;

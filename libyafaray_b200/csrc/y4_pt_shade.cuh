@@ -89,14 +89,22 @@ Y4_HD float y4_fresnel_kr(const Y4PtMaterial &m, const V3 wo, const V3 n)
 	return xmul(xdiv(xmul(xmul(0.5f, gmc), gmc), xmul(gpc, gpc)), xadd(1.f, xdiv(xmul(am, am), xmul(ap, ap))));
 }
 
-// ShinyDiffuseMaterial::accumulate (:123-134) for components {mirror, 0, 0, diffuse}: accum[0] and accum[3]
-Y4_HD void y4_shiny_accumulate(const Y4PtMaterial &m, const V3 wo, const V3 n, float &accum0, float &accum3)
+// ShinyDiffuseMaterial::accumulate (:123-134) for components {mirror, transparency, 0, diffuse}: accum[0], accum[1], accum[3]
+Y4_HD void y4_shiny_accumulate(const Y4PtMaterial &m, const V3 wo, const V3 n, float &accum0, float &accum1, float &accum3)
 {
 	const float kr = y4_fresnel_kr(m, wo, n);
+	const float c1 = m.is_transparent ? m.transparency_strength : 0.f;
 	accum0 = xmul(m.is_mirror ? m.mirror_strength : 0.f, kr);
 	float acc = xsub(1.f, accum0);
-	acc = xmul(acc, xsub(1.f, 0.f)); acc = xmul(acc, xsub(1.f, 0.f));
+	accum1 = xmul(c1, acc);
+	acc = xmul(acc, xsub(1.f, c1)); acc = xmul(acc, xsub(1.f, 0.f));
 	accum3 = xmul(m.is_diffuse ? m.diffuse_strength : 0.f, acc);
+}
+// transmit_filter_strength_ * diffuse colour + (1 - transmit_filter_strength_): the tint of light passing straight through
+Y4_HD C3 y4_shiny_tcol(const Y4PtMaterial &m)
+{
+	const float k = xsub(1.f, m.transmit_filter);
+	return c3(xadd(xmul(m.transmit_filter, m.color.r), k), xadd(xmul(m.transmit_filter, m.color.g), k), xadd(xmul(m.transmit_filter, m.color.b), k));
 }
 
 // Vec3::reflectDir (vector.h:255-260)
@@ -123,25 +131,36 @@ Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, flo
 	}
 	const float cos_ng_wo = xdot(sp.ng, wo);
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
-	float accum0, accum3;
-	y4_shiny_accumulate(m, wo, n, accum0, accum3);
-	// components in c_flags_ order: perfect mirror (Specular | Reflect), then Lambert / Oren-Nayar (Diffuse | Reflect)
-	const uint32_t mflags = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT, dflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
+	float accum0, accum1, accum3;
+	y4_shiny_accumulate(m, wo, n, accum0, accum1, accum3);
+	// components in c_flags_ order: perfect mirror (Specular | Reflect) or straight transmission (Transmit | Filter) -- the host
+	// refuses materials with both --, then Lambert / Oren-Nayar (Diffuse | Reflect)
+	const uint32_t mflags = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT, tflags = Y4_BSDF_TRANSMIT | Y4_BSDF_FILTER, dflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
 	// (scalars instead of the reference's val[] / width[] / choice[] arrays: same arithmetic, no local memory)
-	const bool mm = m.is_mirror && (flags & mflags) == mflags, dm = m.is_diffuse && (flags & dflags) == dflags;
+	const bool mm = m.is_mirror && (flags & mflags) == mflags, tm = !mm && m.is_transparent && (flags & tflags) == tflags;
+	const bool dm = m.is_diffuse && (flags & dflags) == dflags;
+	const float accum_f = mm ? accum0 : accum1;                  // the component in front of the diffuse one
 	float sum = 0.f, val_m = 0.f;
-	if(mm) { sum = xadd(sum, accum0); val_m = sum; }
+	if(mm || tm) { sum = xadd(sum, accum_f); val_m = sum; }
 	if(dm) sum = xadd(sum, accum3);
-	if(!(mm || dm) || sum < 0.00001f) return c3f(1.f);
+	if(!(mm || tm || dm) || sum < 0.00001f) return c3f(1.f);
 	const float inv_sum = xdiv(1.f, sum);
-	const float wm = xmul(accum0, inv_sum), wd = xmul(accum3, inv_sum);
+	const float wm = xmul(accum_f, inv_sum), wd = xmul(accum3, inv_sum);
 	val_m = xmul(val_m, inv_sum);
 	// pick = first matched component with s1 <= val[i], else the last one
-	const bool pick_mirror = mm && (!dm || s1 <= val_m);
-	const float wpick = pick_mirror ? wm : wd;
-	const float s_1 = (!pick_mirror && mm) ? xdiv(xsub(s1, val_m), wpick) : xdiv(s1, wpick);
+	const bool pick_first = (mm || tm) && (!dm || s1 <= val_m);
+	const bool pick_mirror = pick_first && mm;
+	const float wpick = pick_first ? wm : wd;
+	const float s_1 = (!pick_first && (mm || tm)) ? xdiv(xsub(s1, val_m), wpick) : xdiv(s1, wpick);
 	C3 scolor = c3f(0.f);
-	if(pick_mirror)
+	if(pick_first && tm)
+	{
+		wi = xneg(wo);
+		scolor = cscale(y4_shiny_tcol(m), accum1);
+		pdf = (double) fabsf(xdot(wi, n)) < 1e-6 ? 0.f : wpick;
+		specular = true;                                             // sampled_flags_ = Transmit | Filter: counts for the caustic flag
+	}
+	else if(pick_mirror)
 	{
 		wi = y4_reflect_dir(n, wo);
 		pdf = wpick;
@@ -158,7 +177,9 @@ Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, flo
 	}
 	sampled = true;
 	w = xdiv(fabsf(xdot(wi, sp.n)), xadd(xmul(pdf, 0.99f), 0.01f));
-	w = xadd(xmul(w, 1.f), xmul(1.f, xsub(1.f, 1.f)));             // alpha == 1 for opaque materials
+	// getAlpha (:467-488): 1 - (1 - components[0] * kr) * components[1]; 1 for opaque materials
+	const float alpha = m.is_transparent ? xsub(1.f, xmul(xsub(1.f, xmul(m.is_mirror ? m.mirror_strength : 0.f, y4_fresnel_kr(m, wo, n))), m.transparency_strength)) : 1.f;
+	w = xadd(xmul(w, alpha), xmul(1.f, xsub(1.f, alpha)));
 	return scolor;
 }
 
@@ -168,7 +189,7 @@ Y4_HD C3 y4_mat_eval(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, const
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
 	if(xdot(n, wl) < 0.f && !m.flat_material) return c3f(0.f);
 	const float kr = y4_fresnel_kr(m, wo, n);
-	const float m_t = xmul(xsub(1.f, xmul(kr, m.is_mirror ? m.mirror_strength : 0.f)), xsub(1.f, 0.f));
+	const float m_t = xmul(xsub(1.f, xmul(kr, m.is_mirror ? m.mirror_strength : 0.f)), xsub(1.f, m.is_transparent ? m.transparency_strength : 0.f));
 	float m_d = xmul(xmul(m_t, xsub(1.f, 0.f)), m.diffuse_strength);
 	if(m.oren_nayar) m_d = xmul(m_d, y4_oren_nayar(m, wo, wl, n));
 	return cscale(m.color, m_d);
@@ -179,10 +200,11 @@ Y4_HD float y4_mat_pdf(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, con
 	if(m.type == Y4GPU_MAT_LIGHT || !m.is_diffuse) return 0.f;
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
 	// bsdfs = Glossy | Diffuse | Dispersive | Reflect | Transmit hasAny() of both components' flags: the mirror's width counts in the sum
-	float accum0, width;
-	y4_shiny_accumulate(m, wo, n, accum0, width);
+	float accum0, accum1, width;
+	y4_shiny_accumulate(m, wo, n, accum0, accum1, width);
 	float sum = 0.f;
 	if(m.is_mirror) sum = xadd(sum, accum0);
+	if(m.is_transparent) sum = xadd(sum, accum1);
 	sum = xadd(sum, width);
 	const float pdf = xadd(0.f, xmul(fabsf(xdot(wi, n)), width));
 	if(sum < 0.00001f) return 0.f;

@@ -227,7 +227,7 @@ Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
 	v.sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
 	v.m = sc.mats[v.sp.mat];
-	if(!SPEC) { v.m.is_mirror = 0; v.m.fresnel = 0; if(v.m.type == Y4GPU_MAT_MIRROR) v.m.type = Y4GPU_MAT_SHINYDIFFUSE; }
+	if(!SPEC) { v.m.is_mirror = 0; v.m.fresnel = 0; v.m.is_transparent = 0; if(v.m.type == Y4GPU_MAT_MIRROR) v.m.type = Y4GPU_MAT_SHINYDIFFUSE; }
 	if(v.m.layer_count > 0)          // initBsdf evaluates the node chain; getShaderColor / emit() read it (material_shiny_diffuse.cc:237,244)
 	{
 		v.m.color = y4_diffuse_shader_color(sc, v.m, v.sp, h.bu, h.bv, h.prim);
@@ -277,7 +277,7 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 	st3(W.pcol, i, c3f(0.f));
 	st4(W.lsamp, i, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
 	f = Y4_PF_HIT0 | spec;
-	if(vx.m.is_mirror && deeper) f |= Y4_PF_RECURSE;
+	if((vx.m.is_mirror || vx.m.is_transparent) && deeper) f |= Y4_PF_RECURSE;
 	if(vx.m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
 	const uint32_t path_flags = sc.no_recursive ? (uint32_t) Y4_BSDF_ALL : (uint32_t) Y4_BSDF_DIFFUSE;
 	if(sc.n_paths > 0 && (vx.m.bsdf_flags & path_flags)) f |= Y4_PF_PATHS;       // n_paths == 0: DirectLightIntegrator (integrator_direct_light.cc:94-143)
@@ -645,15 +645,25 @@ Y4_HD uint32_t y4_stage_level_finish(const Y4PtScene &sc, const Y4PtWave &W, con
 	const bool backface = xdot(vx.wo, vx.sp.ng) < 0.f;
 	const V3 n = backface ? xneg(vx.sp.n) : vx.sp.n, ng = backface ? xneg(vx.sp.ng) : vx.sp.ng;
 	const float kr = y4_fresnel_kr(vx.m, vx.wo, n);
-	const float vn = xmul(2.f, xdot(vx.wo, n));                                  // Vec3::reflect (vector.h:227-232)
-	V3 dir = v3(xsub(xmul(vn, n.x), vx.wo.x), xsub(xmul(vn, n.y), vx.wo.y), xsub(xmul(vn, n.z), vx.wo.z));
-	const float cos_wi_ng = xdot(dir, ng);
-	if((double) cos_wi_ng < 0.01)
+	V3 dir; C3 w;
+	if(vx.m.is_transparent)
 	{
-		const float k = (float) (0.01 - (double) cos_wi_ng);
-		dir = xnormalize(v3(xadd(dir.x, xmul(k, ng.x)), xadd(dir.y, xmul(k, ng.y)), xadd(dir.z, xmul(k, ng.z))));
+		// refract_: straight on; (1 - components[0] * kr) * components[1] * tcol (specularRefract, transparent bias factor 0)
+		dir = xneg(vx.wo);
+		w = cscale(y4_shiny_tcol(vx.m), xmul(xsub(1.f, xmul(vx.m.is_mirror ? vx.m.mirror_strength : 0.f, kr)), vx.m.transparency_strength));
 	}
-	C3 w = cscale(vx.m.mirror_color, xmul(vx.m.mirror_strength, kr));
+	else
+	{
+		const float vn = xmul(2.f, xdot(vx.wo, n));                                  // Vec3::reflect (vector.h:227-232)
+		dir = v3(xsub(xmul(vn, n.x), vx.wo.x), xsub(xmul(vn, n.y), vx.wo.y), xsub(xmul(vn, n.z), vx.wo.z));
+		const float cos_wi_ng = xdot(dir, ng);
+		if((double) cos_wi_ng < 0.01)
+		{
+			const float k = (float) (0.01 - (double) cos_wi_ng);
+			dir = xnormalize(v3(xadd(dir.x, xmul(k, ng.x)), xadd(dir.y, xmul(k, ng.y)), xadd(dir.z, xmul(k, ng.z))));
+		}
+		w = cscale(vx.m.mirror_color, xmul(vx.m.mirror_strength, kr));
+	}
 	if(f & Y4_PF_SPEC) w = cmul(sw, w);
 	st_ray(W.ray0, i, y4_mk_ray(vx.sp.p, sc.ray_min_dist, dir, -1.f));
 	st4(W.sw, i, f4(w.r, w.g, w.b, y4_u2f((uint32_t) (level + 1))));

@@ -55,6 +55,8 @@ struct Y4PtMaterial
 	// shinydiffusemat's perfect-mirror component (components_[0]): specular_reflect, mirror_color, Fresnel weighting
 	int is_mirror; float mirror_strength; C3 mirror_color;
 	int fresnel; float ior_squared;
+	// shinydiffusemat's straight-through transparency component (components_[1]): transparency, transmit_filter
+	int is_transparent; float transparency_strength, transmit_filter;
 };
 
 // ImageTexture state (texture_image.cc:476-597) + texels as Image::getColor returns them

@@ -200,9 +200,12 @@ class Interface:
         p = dict(self.params)
         t = p.get("type")
         if t == "shinydiffusemat":
-            for k in ("transparency", "translucency"):
-                if float(p.get(k, 0.0)) != 0.0:
-                    raise Y4Error(f"shinydiffusemat '{name}': {k} != 0 is not supported by the GPU back end")
+            if float(p.get("translucency", 0.0)) != 0.0:
+                raise Y4Error(f"shinydiffusemat '{name}': translucency != 0 is not supported by the GPU back end")
+            if float(p.get("transparency", 0.0)) > 0.00001 and float(p.get("specular_reflect", 0.0)) > 0.00001:
+                raise Y4Error(f"shinydiffusemat '{name}': transparency together with specular_reflect is not supported by the GPU back end")
+            if float(p.get("transparentbias_factor", 0.0)) != 0.0:
+                raise Y4Error(f"shinydiffusemat '{name}': transparentbias_factor is not supported by the GPU back end")
             if float(p.get("samplingfactor", 1.0)) != 1.0 or int(p.get("additionaldepth", 0)) != 0:
                 raise Y4Error(f"shinydiffusemat '{name}': samplingfactor / additionaldepth are not supported by the GPU back end")
             if float(p.get("wireframe_amount", 0.0)) != 0.0:
@@ -521,6 +524,7 @@ class Interface:
                 m.type, m.diffuse_reflect, m.emit = _lib.MAT_SHINYDIFFUSE, float(p.get("diffuse_reflect", 1.0)), float(p.get("emit", 0.0))
                 m.specular_reflect, m.fresnel_effect, m.ior = float(p.get("specular_reflect", 0.0)), int(p.get("fresnel_effect", False)), float(p.get("IOR", 1.33))
                 m.mirror_color[:] = p.get("mirror_color", (1.0, 1.0, 1.0, 1.0))[:3]
+                m.transparency, m.transmit_filter = float(p.get("transparency", 0.0)), float(p.get("transmit_filter", 1.0))
                 if p.get("diffuse_brdf", "lambert") == "oren_nayar":
                     m.oren_nayar, m.sigma = 1, float(p.get("sigma", 0.1))
 
@@ -565,7 +569,10 @@ class Interface:
             pr.bounces, pr.path_samples = 1, 0
         pr.russian_roulette_min_bounces, pr.no_recursive = int(integ.get("russian_roulette_min_bounces", 0)), int(integ.get("no_recursive", False))
         pr.transp_background = int(integ.get("bg_transp", False))
-        if pr.no_recursive and any(self.materials[n]["type"] == "mirror" or float(self.materials[n].get("specular_reflect", 0.0)) > 0.00001 for n in mat_names):
+        if integ.get("transpShad", False) and any(float(self.materials[n].get("transparency", 0.0)) > 0.00001 for n in mat_names):
+            raise Y4Error("transparent materials with transpShad are not supported by the GPU back end")
+        if pr.no_recursive and any(self.materials[n]["type"] == "mirror" or float(self.materials[n].get("specular_reflect", 0.0)) > 0.00001
+                                   or float(self.materials[n].get("transparency", 0.0)) > 0.00001 for n in mat_names):
             raise Y4Error("no_recursive with mirror materials / specular_reflect is not supported by the GPU back end")
         pr.raydepth, pr.transp_refracted_background = int(integ.get("raydepth", 5)), int(integ.get("bg_transp_refract", False))
         pr.trace_caustics = int(integ.get("type") == "pathtracing" and integ.get("caustic_type", "path") not in ("none", "photon"))

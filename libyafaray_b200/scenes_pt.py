@@ -84,7 +84,7 @@ def _uv_sphere(centre, radius, nu, nv):
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
                 oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None,
-                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None):
+                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front.
     mirror: {"objects": subset of ("tall", "short", "back", "left", "sphere"), "color": rgb, "reflect": r} -> those objects get a
@@ -92,6 +92,8 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
     extra.update(shiny or {})          # shiny: shinydiffusemat parameters of all three wall materials (specular_reflect, mirror_color, fresnel_effect, IOR)
+    if pane:                           # pane: shinydiffusemat parameters (transparency, transmit_filter, ...) of a sheet across the box at z = 0.45
+        _material(api, "pane", pane.get("color", (0.3, 0.5, 0.9)), **{k: v for k, v in pane.items() if k != "color"})
     _material(api, "white", white, **extra)
     _material(api, "red", red, **extra)
     _material(api, "green", green, **({**extra, "emit": glow} if glow else extra))       # glow: the right wall also emits
@@ -133,6 +135,9 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         v, t = _uv_sphere((0.33, 0.42, 0.35), 0.12, 12, 7)
         _mesh(api, "i_sphere", mat("sphere", "white"), v, t)
         api.smoothMesh("i_sphere", float(smooth_sphere))
+    if pane:
+        v, t = _quad((0.1, 0.05, 0.45), (0.9, 0.05, 0.45), (0.9, 0.8, 0.45), (0.1, 0.8, 0.45))
+        _mesh(api, "j_pane", "pane", v, t)
     api.endGeometry()
 
     api.paramsClearAll()

@@ -85,6 +85,13 @@ PT_GOLDEN_MIRROR = {
     "shiny_fresnel_mirror_box_glow": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, shiny=dict(specular_reflect=0.6, fresnel_effect=True, IOR=1.8),
                                           mirror=dict(objects=("tall",), color=(0.9, 0.95, 0.8)), glow=0.5, oren_nayar=True, path_samples=2, light_samples=2,
                                           integrator_extra=dict(raydepth=2, caustic_type="path")),
+    # shinydiffusemat transparency / transmit_filter: straight-through refraction rays (specularRefract), the Transmit | Filter
+    # lobe inside paths, getAlpha in the sample weight; shadows stay opaque (transpShad off, the reference's default)
+    "pane_filter_glow_caustic": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, pane=dict(transparency=0.8, transmit_filter=0.4, diffuse_reflect=0.7),
+                                     glow=0.5, integrator_extra=dict(raydepth=3, caustic_type="path")),
+    "pane_fresnel_shiny_walls_transp_bg_direct": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, integrator="directlighting",
+                                                      pane=dict(transparency=0.5, fresnel_effect=True), shiny=dict(specular_reflect=0.3), background=(0.3, 0.2, 0.1),
+                                                      integrator_extra=dict(raydepth=3, bg_transp=True, bg_transp_refract=True)),
     "mirror_sphere_transp_bg_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", smooth_sphere=180.0,
                                            mirror=dict(objects=("sphere", "short")), background=(0.3, 0.2, 0.1),
                                            integrator_extra=dict(raydepth=2, bg_transp=True, bg_transp_refract=True)),

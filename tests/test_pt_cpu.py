@@ -118,7 +118,7 @@ def test_interface_rejects_unsupported_features():
         yi.createMaterial("g")
     yi.paramsClearAll()
     yi.paramsSetString("type", "shinydiffusemat")
-    yi.paramsSetFloat("transparency", 0.5)
+    yi.paramsSetFloat("translucency", 0.5)
     with pytest.raises(Y4Error):
         yi.createMaterial("t")
     yi.paramsClearAll()
@@ -304,6 +304,41 @@ def test_shinydiffuse_mirror_component_vs_live_reference(variant):
     img = interface.normalize_film(w, rgba)
     assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
     assert np.abs(img[..., 3] - ref[..., 3]).max() <= 1e-6
+
+
+PANES = [dict(pane=dict(transparency=0.6), integrator_extra=dict(raydepth=0)),                              # lobe sampled in paths only
+         dict(pane=dict(transparency=0.6), integrator_extra=dict(raydepth=2)),
+         dict(pane=dict(transparency=1.0, transmit_filter=1.0, color=(0.9, 0.3, 0.2)), mirror=dict(objects=("tall",)), path_samples=2, light_samples=2,
+              integrator_extra=dict(raydepth=4, caustic_type="path")),
+         dict(pane=dict(transparency=0.7, transmit_filter=0.2), extra_lights=("sphere", "spot"), integrator_extra=dict(raydepth=2, caustic_type="path"))]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("variant", PANES)
+def test_shinydiffuse_transparency_vs_live_reference(variant):
+    """shinydiffusemat transparency / transmit_filter: config / accumulate with components {0 | mirror, transparency, 0, diffuse},
+    the Transmit | Filter lobe of sample(), getAlpha in the sample weight, eval's (1 - transparency) factor, pdf's sum over
+    both components, getSpecular's refract_ (straight on) followed level by level through specularRefract."""
+    kw = dict(width=64, height=36, spp=3, bounces=4, **variant)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    a = _assemble(**kw)
+    w, rgba = helpers.emu_pt_render(a, ref_light_order=a["n_light"] > 1 and a["params"].path_samples > 0)
+    img = interface.normalize_film(w, rgba)
+    assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
+    assert np.abs(img[..., 3] - ref[..., 3]).max() <= 1e-6
+
+
+def test_transparency_combinations_outside_the_chain_model_are_rejected():
+    """reflection + refraction at one vertex (two child rays) and filtered shadows through transparent blockers are refused."""
+    yi = interface.Interface()
+    with pytest.raises(Y4Error, match="specular_reflect"):
+        scenes_pt.cornell_box(yi, width=16, height=9, spp=1, pane=dict(transparency=0.5, specular_reflect=0.2), accelerator="yafaray-b200-bvh8")
+    yi = interface.Interface()
+    scenes_pt.cornell_box(yi, width=16, height=9, spp=1, pane=dict(transparency=0.5), integrator_extra=dict(transpShad=True), accelerator="yafaray-b200-bvh8")
+    with pytest.raises(Y4Error, match="transpShad"):
+        yi.assemble()
 
 
 def test_mirror_with_no_recursive_is_rejected():
