@@ -46,6 +46,7 @@ struct Y4Pt
 	cudaEvent_t ev_fork = nullptr;
 	// per-launch counters: 64-bit slots, zeroed once per pass; a queue length is the low word of its slot
 	unsigned long long *d_counters = nullptr, *h_counters = nullptr; size_t counters_cap = 0;
+	float *d_mat_transp = nullptr; uint32_t mat_transp_cap = 0;   // [n_mat * 3] getTransparency colours (filtered shadows)
 	std::vector<std::pair<uint32_t, int>> counter_kinds;      // (slot, kind) of the last pass: 0 traced path queue, 1 shadow queue, 2 camera-hit queue, 3 closing path queue, 4 ray-level queue (mirror reflections)
 	uint64_t dense_closest = 0;
 	bool counters_read = true;
@@ -260,7 +261,7 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	}
 	for(int l = 1; l < kMaxLanes; ++l) if(pt->lanes[l].stream) cudaStreamDestroy(pt->lanes[l].stream);
 	if(pt->ev_fork) cudaEventDestroy(pt->ev_fork);
-	cudaFree(pt->d_lights); cudaFree(pt->d_mats); cudaFree(pt->d_normals); cudaFree(pt->d_tri_shade);
+	cudaFree(pt->d_mat_transp); cudaFree(pt->d_lights); cudaFree(pt->d_mats); cudaFree(pt->d_normals); cudaFree(pt->d_tri_shade);
 	pt_free_textures(pt);
 	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime); cudaFree(pt->d_sigma_d); cudaFree(pt->d_magic);
 	cudaFree(pt->own_film_w); cudaFree(pt->own_film_rgba); cudaFree(pt->d_pixel_list);
@@ -381,7 +382,8 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		{
 			// reflect + refract at one vertex = two child rays (a tree, not a chain); filtered shadows need the blockers' colours
 			if(mats[m].specular_reflect > 0.00001f) { ctx->err = "shinydiffusemat with both specular_reflect and transparency is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
-			if(params->transp_shadows) { ctx->err = "transparent materials with transpShad are not supported"; return Y4GPU_ERR_UNSUPPORTED; }
+			// filtered shadows take one getTransparency colour per material: a textured diffuse colour would need the blocker's surface point
+			if(params->transp_shadows && mats[m].layer_count > 0) { ctx->err = "textured transparent materials with transpShad are not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 		}
 	// no_recursive makes a mirror hit start sub-paths AND recurse: two branches per vertex, which the linear ray-level chain does not cover
 	if(sc.has_specular && sc.no_recursive) { ctx->err = "no_recursive with mirror materials / specular_reflect is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
@@ -411,6 +413,24 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	}
 	std::vector<Y4PtMaterial> hm(n_mat);
 	for(uint32_t i = 0; i < n_mat; ++i) hm[i] = derive_material(mats[i]);
+	// ShinyDiffuseMaterial::getTransparency (:442-465) per material for filtered shadows: accum = 1; accum *= transparency * accum; accum * tcol
+	sc.tshadow_filter = 0;
+	std::vector<float> mat_transp(3 * (size_t) n_mat, 0.f);
+	for(uint32_t i = 0; i < n_mat; ++i)
+		if(hm[i].is_transparent)
+		{
+			float accum = 1.f; accum *= hm[i].transparency_strength * accum;
+			const C3 tc = y4_shiny_tcol(hm[i]);
+			mat_transp[3 * i] = accum * tc.r; mat_transp[3 * i + 1] = accum * tc.g; mat_transp[3 * i + 2] = accum * tc.b;
+			if(params->transp_shadows) sc.tshadow_filter = 1;
+		}
+	if(sc.tshadow_filter)
+	{
+		if(n_mat > pt->mat_transp_cap) { cudaFree(pt->d_mat_transp); pt->d_mat_transp = nullptr; pt->mat_transp_cap = 0; }
+		if(!pt->d_mat_transp) { Y4_CUDA(ctx, cudaMalloc(&pt->d_mat_transp, 3 * (size_t) n_mat * sizeof(float))); pt->mat_transp_cap = n_mat; }
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_mat_transp, mat_transp.data(), 3 * (size_t) n_mat * sizeof(float), cudaMemcpyHostToDevice, st));
+		Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	}
 	if(n_mat > pt->mats_cap) { cudaFree(pt->d_mats); pt->d_mats = nullptr; pt->mats_cap = 0; }
 	if(!pt->d_mats) { Y4_CUDA(ctx, cudaMalloc(&pt->d_mats, n_mat * sizeof(Y4PtMaterial))); pt->mats_cap = n_mat; }
 	Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_mats, hm.data(), n_mat * sizeof(Y4PtMaterial), cudaMemcpyHostToDevice, st));
@@ -706,7 +726,9 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	{ const int rc_ = mark(-1); if(rc_) return rc_; }
 #define Y4_PT_LAUNCH(cls, ...) do { __VA_ARGS__; ++own_launches; const int rc_ = mark(cls); if(rc_) return rc_; } while(0)
 #define Y4_PT_TRACE(kind, rays, hits, n_max, queue, count) do { \
-		int rc_ = y4_launch_trace_wave(ctx, kind, prof, rays, hits, n_max, queue, count, new_slot(), pt->d_counters + (kind == Y4_TRACE_CLOSEST ? 0 : 3), st, trace_blocks); \
+		int rc_ = (kind == Y4_TRACE_TSHADOW && sc.tshadow_filter) \
+			? y4_launch_tshadow_wave(ctx, rays, hits, queue, count, pt->params.shadow_depth, pt->d_mat_transp, (uint32_t) sc.n_mats, new_slot(), st, trace_blocks) \
+			: y4_launch_trace_wave(ctx, kind, prof, rays, hits, n_max, queue, count, new_slot(), pt->d_counters + (kind == Y4_TRACE_CLOSEST ? 0 : 3), st, trace_blocks); \
 		if(rc_ || (rc_ = mark(kind == Y4_TRACE_CLOSEST ? 1 : 2))) return rc_; } while(0)
 	if(n_lanes > 1)
 	{

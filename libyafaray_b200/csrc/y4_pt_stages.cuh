@@ -364,8 +364,19 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return;
 	// everything this step can need, requested together
 	const float4 zero4 = f4(0.f, 0.f, 0.f, 0.f);
-	const float4 c0 = ld4(W.scontrib, i), c1 = (f & Y4_PF_C1) ? ld4(W.scontrib, n + i) : zero4;
-	const int32_t p0 = (f & Y4_PF_S0) ? W.shit[i].prim : -1, p1 = (f & Y4_PF_S1) ? W.shit[n + i].prim : -1;
+	float4 c0 = ld4(W.scontrib, i), c1 = (f & Y4_PF_C1) ? ld4(W.scontrib, n + i) : zero4;
+	int32_t p0 = -1, p1 = -1;
+	if(sc.tshadow_filter)
+	{
+		// isShadowed(ray, s_depth_, ...) -> scol; "lcol *= scol" (integrator_montecarlo.cc:121,229,335): the product of the transparent
+		// blockers' getTransparency colours scales the sample (applied to the finished product here: <= 1 ulp from the reference's order)
+		if(f & Y4_PF_S0) { const Y4Hit s = ld_hit(W.shit, i); p0 = s.prim; c0.x = xmul(c0.x, s.t); c0.y = xmul(c0.y, s.bu); c0.z = xmul(c0.z, s.bv); }
+		if(f & Y4_PF_S1) { const Y4Hit s = ld_hit(W.shit, n + i); p1 = s.prim; c1.x = xmul(c1.x, s.t); c1.y = xmul(c1.y, s.bu); c1.z = xmul(c1.z, s.bv); }
+	}
+	else
+	{
+		p0 = (f & Y4_PF_S0) ? W.shit[i].prim : -1; p1 = (f & Y4_PF_S1) ? W.shit[n + i].prim : -1;
+	}
 	const float4 base = all_lights ? ld4(W.col, i) : ld4(W.pcol, i);
 	const float4 thr4 = all_lights ? zero4 : ld4(W.pthr, i);
 	const float4 lc4 = (all_lights || !(f & Y4_PF_LCOL)) ? zero4 : ld4(W.lcol, i);

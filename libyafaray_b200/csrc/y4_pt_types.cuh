@@ -106,6 +106,7 @@ struct Y4PtScene
 	// integrator
 	int bounces, n_paths, rr_min_bounces, no_recursive, transp_background;
 	int raydepth, trace_caustics, transp_refracted_background;
+	int tshadow_filter;             // transpShad with transparent materials: shadow hits carry the blockers' filter colour (t, bu, bv lanes)
 	int has_specular;               // ray-level loop (recursiveRaytrace) needed: 1 pure mirrors only (chains run inside the camera-hit
 	                                // step), 2 shinydiffuse with a mirror component (one full estimate per ray level)
 	C3 background;

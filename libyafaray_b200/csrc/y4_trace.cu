@@ -186,6 +186,44 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, con
 	}
 }
 
+// The same over an index queue of the path tracer: the filter colour goes into the hit record's t / bu / bv lanes
+// (prim >= 0: shadowed).  One packet counter per launch (a zeroed 64-bit slot of the pass).
+__global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow_queue(Y4Bvh8 bvh, const Y4Ray *__restrict__ rays, const uint32_t *__restrict__ queue,
+                                                                       const uint32_t *__restrict__ queue_count, int max_depth, const float *__restrict__ mat_transp,
+                                                                       uint32_t n_mat, Y4Hit *__restrict__ out, unsigned long long *__restrict__ work_counter)
+{
+	const uint32_t lane = threadIdx.x & 31u;
+	uint2 stack[Y4_STACK_SIZE];
+	uint32_t filt[16], filt_mat[16];
+	const uint32_t n = *queue_count;
+	const uint32_t n_packets = (n + 31u) >> 5;
+	if(max_depth > 16) max_depth = 16;
+	while(true)
+	{
+		uint32_t packet = 0;
+		if(lane == 0) packet = atomicAdd(reinterpret_cast<uint32_t *>(work_counter), 1u);
+		packet = __shfl_sync(0xffffffffu, packet, 0);
+		if(packet >= n_packets) break;
+		const uint32_t q = (packet << 5) + lane;
+		if(q >= n) continue;
+		const uint32_t i = queue[q];
+		const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + i));
+		const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + i) + 1);
+		Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
+		const Y4PreparedRay pr = y4_prepare_ray(r, Y4_TRACE_TSHADOW);
+		Y4Hit h; h.t = 0.f; h.bu = 0.f; h.bv = 0.f; h.prim = -1;
+		int n_filt = 0;
+		if(pr.t_hi > pr.t_lo) y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, h, stack, nullptr, filt, filt_mat, &n_filt, max_depth);
+		float fr = 1.f, fg = 1.f, fb = 1.f;
+		for(int k = 0; k < n_filt; ++k)
+		{
+			const uint32_t m = filt_mat[k];
+			if(m < n_mat) { fr = __fmul_rn(fr, mat_transp[3 * m]); fg = __fmul_rn(fg, mat_transp[3 * m + 1]); fb = __fmul_rn(fb, mat_transp[3 * m + 2]); }
+		}
+		*reinterpret_cast<float4 *>(out + i) = make_float4(fr, fg, fb, __uint_as_float((uint32_t) h.prim));
+	}
+}
+
 struct TraceArgs
 {
 	const Y4Ray *rays; uint64_t n; Y4Hit *out;
@@ -260,6 +298,16 @@ int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_
 	else if(kind == Y4_TRACE_TSHADOW) rc = d_queue ? launch<Y4_TRACE_TSHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_TSHADOW, false>(ctx, counted, a);
 	else { ctx->err = "bad trace kind"; return Y4GPU_ERR_ARG; }
 	if(rc) return rc;
+	ctx->stats.kernel_launches++;
+	return Y4GPU_OK;
+}
+
+int y4_launch_tshadow_wave(y4gpu_ctx *ctx, const Y4Ray *d_rays, Y4Hit *d_out, const uint32_t *d_queue, const uint32_t *d_queue_count, int max_depth,
+                           const float *d_mat_transp, uint32_t n_mat, unsigned long long *d_work_counter, cudaStream_t stream, int max_blocks_per_sm)
+{
+	const int per_sm = max_blocks_per_sm > 0 && max_blocks_per_sm < 4 ? max_blocks_per_sm : 4;
+	k_trace_tshadow_queue<<<ctx->sm_count * per_sm, kTraceThreads, 0, stream>>>(ctx->view(), d_rays, d_queue, d_queue_count, max_depth, d_mat_transp, n_mat, d_out, d_work_counter);
+	Y4_CUDA(ctx, cudaGetLastError());
 	ctx->stats.kernel_launches++;
 	return Y4GPU_OK;
 }

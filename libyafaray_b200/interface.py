@@ -386,6 +386,8 @@ class Interface:
                     w |= _lib.TRI_VIS_SHADOW
                 if sh_m:
                     w |= _lib.TRI_VIS_TSHADOW
+                if float(self.materials[mn].get("transparency", 0.0)) > 0.00001 and self.materials[mn].get("type") == "shinydiffusemat":
+                    w |= _lib.TRI_TRANSPARENT          # Material::isTransparent(): bsdf_flags_ has Transmit (intersectTs filters instead of blocking)
                 words[mn] = w
             f = np.fromiter((words[mn] for mn in base.tri_mats), np.uint32, len(base.tri_mats))
             nn = None
@@ -569,14 +571,14 @@ class Interface:
             pr.bounces, pr.path_samples = 1, 0
         pr.russian_roulette_min_bounces, pr.no_recursive = int(integ.get("russian_roulette_min_bounces", 0)), int(integ.get("no_recursive", False))
         pr.transp_background = int(integ.get("bg_transp", False))
-        if integ.get("transpShad", False) and any(float(self.materials[n].get("transparency", 0.0)) > 0.00001 for n in mat_names):
-            raise Y4Error("transparent materials with transpShad are not supported by the GPU back end")
+        if integ.get("transpShad", False) and any(float(self.materials[n].get("transparency", 0.0)) > 0.00001 and n in chain_of for n in mat_names):
+            raise Y4Error("textured transparent materials with transpShad are not supported by the GPU back end")
         if pr.no_recursive and any(self.materials[n]["type"] == "mirror" or float(self.materials[n].get("specular_reflect", 0.0)) > 0.00001
                                    or float(self.materials[n].get("transparency", 0.0)) > 0.00001 for n in mat_names):
             raise Y4Error("no_recursive with mirror materials / specular_reflect is not supported by the GPU back end")
         pr.raydepth, pr.transp_refracted_background = int(integ.get("raydepth", 5)), int(integ.get("bg_transp_refract", False))
         pr.trace_caustics = int(integ.get("type") == "pathtracing" and integ.get("caustic_type", "path") not in ("none", "photon"))
-        pr.transp_shadows, pr.shadow_depth = int(bool(integ.get("transpShad", False))), int(integ.get("shadowDepth", 4))
+        pr.transp_shadows, pr.shadow_depth = int(bool(integ.get("transpShad", False))), int(integ.get("shadowDepth", 5))
         if bg is not None:
             c, pw = bg.get("color", (0.0, 0.0, 0.0, 1.0)), np.float32(bg.get("power", 1.0))
             pr.background[:] = [float(np.float32(c[k]) * pw) for k in range(3)]

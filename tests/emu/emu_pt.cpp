@@ -52,6 +52,8 @@ struct EmuBvh
 void emu_build(const float *verts, const uint32_t *flags, int n, int leaf_max, EmuBvh &out);
 
 // queue == null: dense batch of n rays; else n index entries
+static int g_shadow_depth = 16;
+static std::vector<float> g_mat_transp;      // getTransparency colour per material when shadows are filtered (else empty)
 static void trace(const Y4Bvh8 &bvh, int kind, const Y4Ray *rays, const uint32_t *queue, size_t n, Y4Hit *hits)
 {
 	for(size_t q = 0; q < n; ++q)
@@ -64,7 +66,16 @@ static void trace(const Y4Bvh8 &bvh, int kind, const Y4Ray *rays, const uint32_t
 		uint32_t filt[16], filt_mat[16]; int n_filt = 0;
 		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray<Y4_TRACE_CLOSEST>(bvh, pr, hits[i], stack, nullptr, nullptr, nullptr, nullptr, 0);
 		else if(kind == Y4_TRACE_SHADOW) y4_trace_ray<Y4_TRACE_SHADOW>(bvh, pr, hits[i], stack, nullptr, nullptr, nullptr, nullptr, 0);
-		else y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, hits[i], stack, nullptr, filt, filt_mat, &n_filt, 16);
+		else
+		{
+			y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, hits[i], stack, nullptr, filt, filt_mat, &n_filt, g_shadow_depth < 16 ? g_shadow_depth : 16);
+			if(!g_mat_transp.empty())       // k_trace_tshadow_queue: the filter colour travels in the t / bu / bv lanes
+			{
+				float fc[3] = {1.f, 1.f, 1.f};
+				for(int k = 0; k < n_filt; ++k) for(int c = 0; c < 3; ++c) fc[c] *= g_mat_transp[3 * filt_mat[k] + c];
+				hits[i].t = fc[0]; hits[i].bu = fc[1]; hits[i].bv = fc[2];
+			}
+		}
 	}
 }
 
@@ -128,6 +139,16 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	for(int t = 0; t < n_tri; ++t) tri_shade[t] = y4_tri_shade(verts, flags, n_mat, (uint64_t) t);
 	std::vector<Y4PtMaterial> hm(n_mat);
 	for(uint32_t i = 0; i < n_mat; ++i) hm[i] = derive_material(mats[i]);
+	sc.tshadow_filter = 0; g_mat_transp.clear(); g_shadow_depth = params->transp_shadows ? params->shadow_depth : 16;
+	for(uint32_t i = 0; i < n_mat; ++i)
+		if(hm[i].is_transparent && params->transp_shadows)      // as y4gpu_pt_set_scene
+		{
+			if(g_mat_transp.empty()) g_mat_transp.assign(3 * (size_t) n_mat, 0.f);
+			float accum = 1.f; accum *= hm[i].transparency_strength * accum;
+			const C3 tc = y4_shiny_tcol(hm[i]);
+			g_mat_transp[3 * i] = accum * tc.r; g_mat_transp[3 * i + 1] = accum * tc.g; g_mat_transp[3 * i + 2] = accum * tc.b;
+			sc.tshadow_filter = 1;
+		}
 	sc.lights = hl.data(); sc.mats = hm.data(); sc.tri_shade = tri_shade.data(); sc.normals = normals;
 	sc.textures = g_textures.empty() ? nullptr : g_textures.data(); sc.layers = g_layers.empty() ? nullptr : g_layers.data();
 	sc.tri_orco = g_tri_orco.empty() ? nullptr : g_tri_orco.data(); sc.tri_uv = g_tri_uv.empty() ? nullptr : g_tri_uv.data();

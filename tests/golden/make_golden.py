@@ -92,6 +92,10 @@ PT_GOLDEN_MIRROR = {
     "pane_fresnel_shiny_walls_transp_bg_direct": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, integrator="directlighting",
                                                       pane=dict(transparency=0.5, fresnel_effect=True), shiny=dict(specular_reflect=0.3), background=(0.3, 0.2, 0.1),
                                                       integrator_extra=dict(raydepth=3, bg_transp=True, bg_transp_refract=True)),
+    # transpShad: shadow rays filtered by the transparent pane (intersectTs colour product, shadowDepth)
+    "pane_filtered_shadows": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, light_samples=2, path_samples=2,
+                                  pane=dict(transparency=0.9, transmit_filter=1.0, color=(0.9, 0.3, 0.2)),
+                                  integrator_extra=dict(raydepth=3, transpShad=True, caustic_type="path")),
     "mirror_sphere_transp_bg_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", smooth_sphere=180.0,
                                            mirror=dict(objects=("sphere", "short")), background=(0.3, 0.2, 0.1),
                                            integrator_extra=dict(raydepth=2, bg_transp=True, bg_transp_refract=True)),
