@@ -266,7 +266,8 @@ typedef struct y4gpu_pt_params
 	int32_t trace_caustics;       /* caustic_type path / both: emission found after a specular bounce of a path counts
 	                                 (integrator_path_tracer.cc:227,256-264) */
 	int32_t transp_refracted_background;   /* bg_transp_refract (TiledIntegrator::background, integrator_tiled.cc:707-720) */
-	int32_t reserved[1];
+	int32_t background_gradient;  /* 0: `constant` background (colour in `background`); 1: `gradientback` (background_gradient.cc:34-46) */
+	float bg_gradient[4][3];      /* gradientback colours * power: zenith_ground, horizon_ground, zenith, horizon */
 } y4gpu_pt_params;
 
 typedef struct y4gpu_pt_stats

@@ -370,6 +370,9 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	sc.cam = derive_camera(*cam);
 	sc.bounces = params->bounces; sc.n_paths = params->path_samples; sc.rr_min_bounces = params->russian_roulette_min_bounces;
 	sc.no_recursive = params->no_recursive; sc.transp_background = params->transp_background;
+	sc.bg_gradient = params->background_gradient;
+	sc.bg_gz = c3(params->bg_gradient[0][0], params->bg_gradient[0][1], params->bg_gradient[0][2]); sc.bg_gh = c3(params->bg_gradient[1][0], params->bg_gradient[1][1], params->bg_gradient[1][2]);
+	sc.bg_sz = c3(params->bg_gradient[2][0], params->bg_gradient[2][1], params->bg_gradient[2][2]); sc.bg_sh = c3(params->bg_gradient[3][0], params->bg_gradient[3][1], params->bg_gradient[3][2]);
 	sc.raydepth = params->raydepth; sc.trace_caustics = params->trace_caustics; sc.transp_refracted_background = params->transp_refracted_background;
 	sc.has_specular = 0;
 	for(uint32_t m = 0; m < n_mat; ++m)

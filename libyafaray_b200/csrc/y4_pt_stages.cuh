@@ -243,6 +243,22 @@ Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 // reflected ray was written to W.ray0 (recursiveRaytrace -> specularReflect -> integrate at level + 1,
 // integrator_montecarlo.cc:868-964; the chain's colour factors are multiplied up front into W.sw and applied when the
 // pixel-sample is splatted: same factors as the reference's unwinding products, in the opposite order).
+// (*background)(ray.dir_): ConstantBackground::eval / GradientBackground::eval (background_gradient.cc:34-46)
+Y4_HD C3 y4_background(const Y4PtScene &sc, const V3 dir)
+{
+	if(!sc.bg_gradient) return sc.background;
+	float blend = dir.z;
+	C3 color;
+	if(blend >= 0.f) color = cadd(cscale(sc.bg_sz, blend), cscale(sc.bg_sh, xsub(1.f, blend)));
+	else
+	{
+		blend = -blend;
+		color = cadd(cscale(sc.bg_gz, blend), cscale(sc.bg_gh, xsub(1.f, blend)));
+	}
+	if(fminf(color.r, fminf(color.g, color.b)) < 1e-6f) color = c3f(1e-5f);
+	return color;
+}
+
 template<bool SPEC = true>
 Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int level, uint32_t &f, Y4Vertex &vx)
 {
@@ -252,7 +268,7 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 	if(h.prim < 0)
 	{
 		const bool transp = sc.transp_background != 0 && (level == 0 || sc.transp_refracted_background != 0);   // TiledIntegrator::background
-		const C3 bg = transp ? c3f(0.f) : sc.background;
+		const C3 bg = transp ? c3f(0.f) : y4_background(sc, v3(r.dx, r.dy, r.dz));
 		st4(W.col, i, f4(bg.r, bg.g, bg.b, transp ? 0.f : 1.f));
 		f = spec;
 		return 0;

@@ -110,6 +110,7 @@ struct Y4PtScene
 	int has_specular;               // ray-level loop (recursiveRaytrace) needed: 1 pure mirrors only (chains run inside the camera-hit
 	                                // step), 2 shinydiffuse with a mirror component (one full estimate per ray level)
 	C3 background;
+	int bg_gradient; C3 bg_gz, bg_gh, bg_sz, bg_sh;     // gradientback: ground zenith / horizon, sky zenith / horizon
 	float shadow_bias; int shadow_bias_auto;
 	float ray_min_dist; int ray_min_dist_auto;
 	uint32_t base_sampling_offset, rr_seed;

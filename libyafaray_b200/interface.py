@@ -240,8 +240,8 @@ class Interface:
 
     def createBackground(self, name):
         p = dict(self.params)
-        if p.get("type") != "constant" or p.get("ibl", False):
-            raise Y4Error("only a constant background without IBL is supported by the GPU back end")
+        if p.get("type") not in ("constant", "gradientback") or p.get("ibl", False):
+            raise Y4Error("only constant / gradientback backgrounds without IBL are supported by the GPU back end")
         self.backgrounds[name] = p
         return True
 
@@ -582,6 +582,12 @@ class Interface:
         if bg is not None:
             c, pw = bg.get("color", (0.0, 0.0, 0.0, 1.0)), np.float32(bg.get("power", 1.0))
             pr.background[:] = [float(np.float32(c[k]) * pw) for k in range(3)]
+            if bg.get("type") == "gradientback":        # GradientBackground::factory (background_gradient.cc:49-77): ground colours default to the sky's
+                sh, sz = bg.get("horizon_color", (1.0, 1.0, 1.0, 1.0)), bg.get("zenith_color", (0.4, 0.5, 1.0, 1.0))
+                gh, gz = bg.get("horizon_ground_color", sh), bg.get("zenith_ground_color", sz)
+                pr.background_gradient = 1
+                for j, col in enumerate((gz, gh, sz, sh)):
+                    pr.bg_gradient[j][:] = [float(np.float32(col[k]) * pw) for k in range(3)]
         if not rp.get("background_resampling", True):
             raise Y4Error("background_resampling=false is not supported by the GPU back end")
         pr.width, pr.height = int(rp.get("width", cam.resx)), int(rp.get("height", cam.resy))

@@ -213,8 +213,11 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     api.createCamera("cam")
 
     api.paramsClearAll()
-    api.paramsSetString("type", "constant")
-    api.paramsSetColor("color", *background, 1.0)
+    if isinstance(background, dict):    # another background type with its parameters, e.g. gradientback
+        _set_params(api, background)
+    else:
+        api.paramsSetString("type", "constant")
+        api.paramsSetColor("color", *background, 1.0)
     api.createBackground("bg")
 
     api.paramsClearAll()

@@ -341,6 +341,21 @@ def test_transparency_combinations_outside_the_chain_model_are_rejected():
         scenes_pt.cornell_box(yi, width=16, height=9, spp=1, pane=dict(transparency=0.5, specular_reflect=0.2), accelerator="yafaray-b200-bvh8")
 
 
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+def test_gradient_background_vs_live_reference():
+    """GradientBackground::eval (sky / ground blend on dir.z, the 1e-6 floor) seen directly by an equirectangular camera; the
+    ground colours default to the sky colours."""
+    for bg in ({"type": "gradientback", "horizon_color": (1.0, 0.8, 0.6, 1.0), "zenith_color": (0.2, 0.4, 0.9, 1.0), "horizon_ground_color": (0.3, 0.25, 0.2, 1.0), "power": 0.8},
+               {"type": "gradientback", "zenith_color": (0.0, 0.0, 0.0, 1.0)}):
+        kw = dict(width=64, height=36, spp=3, bounces=3, background=bg,
+                  camera_extra=dict(type="equirectangular", **{"from": (0.5, 0.5, -0.6), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, -0.6)}))
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        ref, _ = helpers.ref_render(rec)
+        w, rgba = helpers.emu_pt_render(_assemble(**kw))
+        assert helpers.psnr(interface.normalize_film(w, rgba), ref) >= 100.0
+
+
 def test_mirror_with_no_recursive_is_rejected():
     """no_recursive makes a mirror hit both start sub-paths and recurse (two branches per vertex): not covered, so refused."""
     yi = interface.Interface()
