@@ -157,6 +157,8 @@ typedef struct y4gpu_pt_material
 	float ior;                    /* shinydiffusemat `IOR` (default 1.33) */
 	float transparency;           /* shinydiffusemat `transparency` (default 0): light passes straight through, tinted by the filter */
 	float transmit_filter;        /* shinydiffusemat `transmit_filter` (default 1): share of the diffuse colour in that tint */
+	float translucency;           /* shinydiffusemat `translucency` (default 0): diffuse transmission to the other side */
+	int32_t reserved[3];
 } y4gpu_pt_material;
 
 /* Image textures and the `diffuse_shader` node chains of shinydiffusemat: texture_mapper + layer nodes

@@ -41,7 +41,8 @@ class PtMaterial(C.Structure):
     _fields_ = [("type", C.c_int32), ("color", C.c_float * 3), ("diffuse_reflect", C.c_float), ("emit", C.c_float),
                 ("oren_nayar", C.c_int32), ("sigma", C.c_float), ("double_sided", C.c_int32), ("receive_shadows", C.c_int32),
                 ("flat_material", C.c_int32), ("layer_first", C.c_int32), ("layer_count", C.c_int32), ("specular_reflect", C.c_float),
-                ("mirror_color", C.c_float * 3), ("fresnel_effect", C.c_int32), ("ior", C.c_float), ("transparency", C.c_float), ("transmit_filter", C.c_float)]  # fmt: skip
+                ("mirror_color", C.c_float * 3), ("fresnel_effect", C.c_int32), ("ior", C.c_float), ("transparency", C.c_float), ("transmit_filter", C.c_float),
+                ("translucency", C.c_float), ("reserved", C.c_int32 * 3)]  # fmt: skip
 
 
 class PtTexture(C.Structure):

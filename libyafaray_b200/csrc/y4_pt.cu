@@ -378,6 +378,8 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	for(uint32_t m = 0; m < n_mat; ++m)
 	{
 		if(mats[m].type == Y4GPU_MAT_MIRROR && !sc.has_specular) sc.has_specular = 1;
+		// translucency needs the full material code (the no-specular kernel variant folds it away), not the ray levels
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].translucency > 0.00001f && !sc.has_specular) sc.has_specular = 1;
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f)) sc.has_specular = 2;
 	}
 	for(uint32_t m = 0; m < n_mat; ++m)

@@ -119,6 +119,12 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 		acc *= 1.f - m.transparency;
 		o.bsdf_flags |= Y4_BSDF_TRANSMIT | Y4_BSDF_FILTER;
 	}
+	if(m.translucency * acc > 0.00001f)
+	{
+		o.is_translucent = 1; o.translucency_strength = m.translucency;
+		acc *= 1.f - m.transparency;                       // sic: config() takes the transparency strength here (:66)
+		o.bsdf_flags |= Y4_BSDF_DIFFUSE | Y4_BSDF_TRANSMIT;
+	}
 	if(m.diffuse_reflect * acc > 0.00001f)
 	{
 		o.is_diffuse = 1; o.diffuse_strength = m.diffuse_reflect;

@@ -89,15 +89,17 @@ Y4_HD float y4_fresnel_kr(const Y4PtMaterial &m, const V3 wo, const V3 n)
 	return xmul(xdiv(xmul(xmul(0.5f, gmc), gmc), xmul(gpc, gpc)), xadd(1.f, xdiv(xmul(am, am), xmul(ap, ap))));
 }
 
-// ShinyDiffuseMaterial::accumulate (:123-134) for components {mirror, transparency, 0, diffuse}: accum[0], accum[1], accum[3]
-Y4_HD void y4_shiny_accumulate(const Y4PtMaterial &m, const V3 wo, const V3 n, float &accum0, float &accum1, float &accum3)
+// ShinyDiffuseMaterial::accumulate (:123-134) for components {mirror, transparency, translucency, diffuse}
+Y4_HD void y4_shiny_accumulate(const Y4PtMaterial &m, const V3 wo, const V3 n, float &accum0, float &accum1, float &accum2, float &accum3)
 {
 	const float kr = y4_fresnel_kr(m, wo, n);
-	const float c1 = m.is_transparent ? m.transparency_strength : 0.f;
+	const float c1 = m.is_transparent ? m.transparency_strength : 0.f, c2 = m.is_translucent ? m.translucency_strength : 0.f;
 	accum0 = xmul(m.is_mirror ? m.mirror_strength : 0.f, kr);
 	float acc = xsub(1.f, accum0);
 	accum1 = xmul(c1, acc);
-	acc = xmul(acc, xsub(1.f, c1)); acc = xmul(acc, xsub(1.f, 0.f));
+	acc = xmul(acc, xsub(1.f, c1));
+	accum2 = xmul(c2, acc);
+	acc = xmul(acc, xsub(1.f, c2));
 	accum3 = xmul(m.is_diffuse ? m.diffuse_strength : 0.f, acc);
 }
 // transmit_filter_strength_ * diffuse colour + (1 - transmit_filter_strength_): the tint of light passing straight through
@@ -131,42 +133,53 @@ Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, flo
 	}
 	const float cos_ng_wo = xdot(sp.ng, wo);
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
-	float accum0, accum1, accum3;
-	y4_shiny_accumulate(m, wo, n, accum0, accum1, accum3);
+	float accum0, accum1, accum2, accum3;
+	y4_shiny_accumulate(m, wo, n, accum0, accum1, accum2, accum3);
 	// components in c_flags_ order: perfect mirror (Specular | Reflect) or straight transmission (Transmit | Filter) -- the host
-	// refuses materials with both --, then Lambert / Oren-Nayar (Diffuse | Reflect)
-	const uint32_t mflags = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT, tflags = Y4_BSDF_TRANSMIT | Y4_BSDF_FILTER, dflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
+	// refuses materials with both --, translucency (Diffuse | Transmit), Lambert / Oren-Nayar (Diffuse | Reflect)
+	const uint32_t mflags = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT, tflags = Y4_BSDF_TRANSMIT | Y4_BSDF_FILTER;
+	const uint32_t lflags = Y4_BSDF_DIFFUSE | Y4_BSDF_TRANSMIT, dflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
 	// (scalars instead of the reference's val[] / width[] / choice[] arrays: same arithmetic, no local memory)
 	const bool mm = m.is_mirror && (flags & mflags) == mflags, tm = !mm && m.is_transparent && (flags & tflags) == tflags;
-	const bool dm = m.is_diffuse && (flags & dflags) == dflags;
-	const float accum_f = mm ? accum0 : accum1;                  // the component in front of the diffuse one
-	float sum = 0.f, val_m = 0.f;
-	if(mm || tm) { sum = xadd(sum, accum_f); val_m = sum; }
+	const bool fm = mm || tm;                                    // the component in front of the two diffuse ones
+	const bool lm = m.is_translucent && (flags & lflags) == lflags, dm = m.is_diffuse && (flags & dflags) == dflags;
+	const float accum_f = mm ? accum0 : accum1;
+	float sum = 0.f, val_f = 0.f, val_l = 0.f;
+	if(fm) { sum = xadd(sum, accum_f); val_f = sum; }
+	if(lm) { sum = xadd(sum, accum2); val_l = sum; }
 	if(dm) sum = xadd(sum, accum3);
-	if(!(mm || tm || dm) || sum < 0.00001f) return c3f(1.f);
+	if(!(fm || lm || dm) || sum < 0.00001f) return c3f(1.f);
 	const float inv_sum = xdiv(1.f, sum);
-	const float wm = xmul(accum_f, inv_sum), wd = xmul(accum3, inv_sum);
-	val_m = xmul(val_m, inv_sum);
-	// pick = first matched component with s1 <= val[i], else the last one
-	const bool pick_first = (mm || tm) && (!dm || s1 <= val_m);
-	const bool pick_mirror = pick_first && mm;
-	const float wpick = pick_first ? wm : wd;
-	const float s_1 = (!pick_first && (mm || tm)) ? xdiv(xsub(s1, val_m), wpick) : xdiv(s1, wpick);
+	const float wf = xmul(accum_f, inv_sum), wl = xmul(accum2, inv_sum), wd = xmul(accum3, inv_sum);
+	val_f = xmul(val_f, inv_sum); val_l = xmul(val_l, inv_sum);
+	// pick = first matched component with s1 <= val[i], else the last matched one
+	const int pick = (fm && s1 <= val_f) ? 0 : ((lm && s1 <= val_l) ? 1 : (dm ? 2 : (lm ? 1 : 0)));
+	const float wpick = pick == 0 ? wf : (pick == 1 ? wl : wd);
+	// s_1 = (s1 - val[previous matched]) / width, or s1 / width for the first matched component
+	const bool has_prev = pick == 1 ? fm : (pick == 2 ? (lm || fm) : false);
+	const float prev = pick == 1 ? val_f : (lm ? val_l : val_f);
+	const float s_1 = has_prev ? xdiv(xsub(s1, prev), wpick) : xdiv(s1, wpick);
 	C3 scolor = c3f(0.f);
-	if(pick_first && tm)
+	if(pick == 0 && tm)
 	{
 		wi = xneg(wo);
 		scolor = cscale(y4_shiny_tcol(m), accum1);
 		pdf = (double) fabsf(xdot(wi, n)) < 1e-6 ? 0.f : wpick;
 		specular = true;                                             // sampled_flags_ = Transmit | Filter: counts for the caustic flag
 	}
-	else if(pick_mirror)
+	else if(pick == 0)
 	{
 		wi = y4_reflect_dir(n, wo);
 		pdf = wpick;
 		scolor = cscale(m.mirror_color, accum0);
 		scolor = cscale(scolor, xdiv(1.f, fmaxf(fabsf(xdot(sp.n, wi)), 1.0e-6f)));
 		specular = true;
+	}
+	else if(pick == 1)
+	{
+		wi = y4_cos_hemisphere(xneg(n), sp.nu, sp.nv, s_1, s2);
+		if(xmul(cos_ng_wo, xdot(sp.ng, wi)) < 0.f) scolor = cscale(m.color, accum2);
+		pdf = xmul(fabsf(xdot(wi, n)), wpick);
 	}
 	else
 	{
@@ -185,28 +198,35 @@ Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, flo
 
 Y4_HD C3 y4_mat_eval(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, const V3 wl)
 {
-	if(m.type == Y4GPU_MAT_LIGHT || !m.is_diffuse) return c3f(0.f);     // Material::eval default / no Diffuse flag
+	if(m.type == Y4GPU_MAT_LIGHT || !(m.bsdf_flags & Y4_BSDF_DIFFUSE)) return c3f(0.f);     // Material::eval default / no Diffuse flag
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
-	if(xdot(n, wl) < 0.f && !m.flat_material) return c3f(0.f);
 	const float kr = y4_fresnel_kr(m, wo, n);
 	const float m_t = xmul(xsub(1.f, xmul(kr, m.is_mirror ? m.mirror_strength : 0.f)), xsub(1.f, m.is_transparent ? m.transparency_strength : 0.f));
-	float m_d = xmul(xmul(m_t, xsub(1.f, 0.f)), m.diffuse_strength);
+	const float c2 = m.is_translucent ? m.translucency_strength : 0.f;
+	// light from the other side of the surface: the translucency component answers (and nothing else)
+	if(m.is_translucent && xmul(xdot(sp.ng, wo), xdot(sp.ng, wl)) < 0.f) return cscale(m.color, xmul(c2, m_t));
+	if(xdot(n, wl) < 0.f && !m.flat_material) return c3f(0.f);
+	float m_d = xmul(xmul(m_t, xsub(1.f, c2)), m.is_diffuse ? m.diffuse_strength : 0.f);
 	if(m.oren_nayar) m_d = xmul(m_d, y4_oren_nayar(m, wo, wl, n));
 	return cscale(m.color, m_d);
 }
 
 Y4_HD float y4_mat_pdf(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, const V3 wi)
 {
-	if(m.type == Y4GPU_MAT_LIGHT || !m.is_diffuse) return 0.f;
+	if(m.type == Y4GPU_MAT_LIGHT || !(m.bsdf_flags & Y4_BSDF_DIFFUSE)) return 0.f;
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
-	// bsdfs = Glossy | Diffuse | Dispersive | Reflect | Transmit hasAny() of both components' flags: the mirror's width counts in the sum
-	float accum0, accum1, width;
-	y4_shiny_accumulate(m, wo, n, accum0, accum1, width);
-	float sum = 0.f;
+	// bsdfs = Glossy | Diffuse | Dispersive | Reflect | Transmit hasAny() of every component's flags: all widths count in the sum
+	float accum0, accum1, accum2, width;
+	y4_shiny_accumulate(m, wo, n, accum0, accum1, accum2, width);
+	float sum = 0.f, pdf = 0.f;
 	if(m.is_mirror) sum = xadd(sum, accum0);
 	if(m.is_transparent) sum = xadd(sum, accum1);
-	sum = xadd(sum, width);
-	const float pdf = xadd(0.f, xmul(fabsf(xdot(wi, n)), width));
+	if(m.is_translucent)
+	{
+		sum = xadd(sum, accum2);
+		if(xmul(xdot(sp.ng, wo), xdot(sp.ng, wi)) < 0.f) pdf = xadd(pdf, xmul(fabsf(xdot(wi, n)), accum2));
+	}
+	if(m.is_diffuse) { sum = xadd(sum, width); pdf = xadd(pdf, xmul(fabsf(xdot(wi, n)), width)); }
 	if(sum < 0.00001f) return 0.f;
 	return xdiv(pdf, sum);
 }

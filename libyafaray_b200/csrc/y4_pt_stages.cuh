@@ -227,7 +227,7 @@ Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 	const V3 o = v3(r.ox, r.oy, r.oz), d = v3(r.dx, r.dy, r.dz);
 	v.sp = y4_surface(sc, o, d, h.t, h.bu, h.bv, h.prim);
 	v.m = sc.mats[v.sp.mat];
-	if(!SPEC) { v.m.is_mirror = 0; v.m.fresnel = 0; v.m.is_transparent = 0; if(v.m.type == Y4GPU_MAT_MIRROR) v.m.type = Y4GPU_MAT_SHINYDIFFUSE; }
+	if(!SPEC) { v.m.is_mirror = 0; v.m.fresnel = 0; v.m.is_transparent = 0; v.m.is_translucent = 0; if(v.m.type == Y4GPU_MAT_MIRROR) v.m.type = Y4GPU_MAT_SHINYDIFFUSE; }
 	if(v.m.layer_count > 0)          // initBsdf evaluates the node chain; getShaderColor / emit() read it (material_shiny_diffuse.cc:237,244)
 	{
 		v.m.color = y4_diffuse_shader_color(sc, v.m, v.sp, h.bu, h.bv, h.prim);
@@ -485,13 +485,13 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 	{
 		if(m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIFF1; else f &= ~(uint32_t) Y4_PF_DIFF1;
 		if(m.bsdf_flags & Y4_BSDF_EMIT) { emit = y4_mat_emit(m, vx.sp, vx.wo); f |= Y4_PF_EMIT1; } else f &= ~(uint32_t) Y4_PF_EMIT1;
-		direct = m.is_diffuse != 0;     // a non-diffuse vertex evaluates to exactly 0 for every light sample
+		direct = (m.bsdf_flags & Y4_BSDF_DIFFUSE) != 0;     // a vertex without the Diffuse flag evaluates to exactly 0 for every light sample
 		// neither flag: no later vertex of this sub-path can add anything (light estimates need DIFF1, emission EMIT1)
 		if(!(f & (Y4_PF_DIFF1 | Y4_PF_EMIT1))) return 0;
 	}
 	else
 	{
-		direct = (f & Y4_PF_DIFF1) && m.is_diffuse;
+		direct = (f & Y4_PF_DIFF1) && (m.bsdf_flags & Y4_BSDF_DIFFUSE);
 		if(depth > sc.rr_min_bounces)
 		{
 			// the reference draws from a rand()-seeded per-tile generator (not reproducible); documented substitute

@@ -57,6 +57,7 @@ struct Y4PtMaterial
 	int fresnel; float ior_squared;
 	// shinydiffusemat's straight-through transparency component (components_[1]): transparency, transmit_filter
 	int is_transparent; float transparency_strength, transmit_filter;
+	int is_translucent; float translucency_strength;              // components_[2]: diffuse transmission
 };
 
 // ImageTexture state (texture_image.cc:476-597) + texels as Image::getColor returns them

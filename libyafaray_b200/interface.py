@@ -200,8 +200,6 @@ class Interface:
         p = dict(self.params)
         t = p.get("type")
         if t == "shinydiffusemat":
-            if float(p.get("translucency", 0.0)) != 0.0:
-                raise Y4Error(f"shinydiffusemat '{name}': translucency != 0 is not supported by the GPU back end")
             if float(p.get("transparency", 0.0)) > 0.00001 and float(p.get("specular_reflect", 0.0)) > 0.00001:
                 raise Y4Error(f"shinydiffusemat '{name}': transparency together with specular_reflect is not supported by the GPU back end")
             if float(p.get("transparentbias_factor", 0.0)) != 0.0:
@@ -527,6 +525,7 @@ class Interface:
                 m.specular_reflect, m.fresnel_effect, m.ior = float(p.get("specular_reflect", 0.0)), int(p.get("fresnel_effect", False)), float(p.get("IOR", 1.33))
                 m.mirror_color[:] = p.get("mirror_color", (1.0, 1.0, 1.0, 1.0))[:3]
                 m.transparency, m.transmit_filter = float(p.get("transparency", 0.0)), float(p.get("transmit_filter", 1.0))
+                m.translucency = float(p.get("translucency", 0.0))
                 if p.get("diffuse_brdf", "lambert") == "oren_nayar":
                     m.oren_nayar, m.sigma = 1, float(p.get("sigma", 0.1))
 

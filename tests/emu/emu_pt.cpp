@@ -124,6 +124,8 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	for(uint32_t m = 0; m < n_mat; ++m)
 	{
 		if(mats[m].type == Y4GPU_MAT_MIRROR && !sc.has_specular) sc.has_specular = 1;
+		// translucency needs the full material code (the no-specular kernel variant folds it away), not the ray levels
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].translucency > 0.00001f && !sc.has_specular) sc.has_specular = 1;
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f)) sc.has_specular = 2;
 	}
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);

@@ -96,6 +96,9 @@ PT_GOLDEN_MIRROR = {
     "pane_filtered_shadows": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, light_samples=2, path_samples=2,
                                   pane=dict(transparency=0.9, transmit_filter=1.0, color=(0.9, 0.3, 0.2)),
                                   integrator_extra=dict(raydepth=3, transpShad=True, caustic_type="path")),
+    # shinydiffusemat translucency (diffuse transmission) with transparency and Oren-Nayar on the same sheet
+    "pane_translucent_transparent": dict(scene="cornell", width=64, height=36, spp=3, bounces=4, oren_nayar=True,
+                                         pane=dict(translucency=0.6, transparency=0.3, transmit_filter=0.5), integrator_extra=dict(raydepth=2, caustic_type="path")),
     "gradient_background_mirrors": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, mirror=dict(objects=("tall", "back")), integrator_extra=dict(raydepth=3),
                                         background={"type": "gradientback", "horizon_color": (1.0, 0.8, 0.6, 1.0), "zenith_color": (0.2, 0.4, 0.9, 1.0),
                                                     "horizon_ground_color": (0.3, 0.25, 0.2, 1.0), "zenith_ground_color": (0.05, 0.1, 0.02, 1.0), "power": 0.8}),

@@ -118,7 +118,8 @@ def test_interface_rejects_unsupported_features():
         yi.createMaterial("g")
     yi.paramsClearAll()
     yi.paramsSetString("type", "shinydiffusemat")
-    yi.paramsSetFloat("translucency", 0.5)
+    yi.paramsSetFloat("transparency", 0.5)
+    yi.paramsSetFloat("specular_reflect", 0.5)      # refraction + reflection at one vertex: two child rays
     with pytest.raises(Y4Error):
         yi.createMaterial("t")
     yi.paramsClearAll()
@@ -332,6 +333,26 @@ def test_shinydiffuse_transparency_vs_live_reference(variant):
     img = interface.normalize_film(w, rgba)
     assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
     assert np.abs(img[..., 3] - ref[..., 3]).max() <= 1e-6
+
+
+TRANSLUCENT = [dict(pane=dict(translucency=0.5, diffuse_reflect=0.8, color=(0.9, 0.8, 0.3)), light_samples=2, path_samples=2),
+               dict(pane=dict(translucency=0.9, diffuse_reflect=0.0), extra_lights=("sphere", "spot"), point_light=True),      # no Lambert component at all
+               dict(pane=dict(translucency=0.4, specular_reflect=0.3, fresnel_effect=True), integrator="directlighting", integrator_extra=dict(raydepth=2))]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("variant", TRANSLUCENT)
+def test_shinydiffuse_translucency_vs_live_reference(variant):
+    """shinydiffusemat translucency: the Diffuse | Transmit component of config (with its transparency-strength slip) /
+    accumulate / sample (cosine lobe about -n) / eval (light from the far side) / pdf, in the camera-hit sample, the bounce
+    loop and the MIS material sample."""
+    kw = dict(width=64, height=36, spp=3, bounces=4, **variant)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    a = _assemble(**kw)
+    w, rgba = helpers.emu_pt_render(a, ref_light_order=a["n_light"] > 1 and a["params"].path_samples > 0)
+    assert helpers.psnr(interface.normalize_film(w, rgba), ref) >= 100.0
 
 
 def test_transparency_combinations_outside_the_chain_model_are_rejected():
