@@ -51,10 +51,23 @@ Y4_HD float y4_ri_s(uint32_t i, uint32_t r)
 		if(i & 1u) r ^= v;
 	return y4_clamp01((float) ((double) r * (double) Y4_2M32));
 }
+// Larcher-Pillichshammer radical inverse, sample::riLp (sample.h): "for(v = 1 << 31; i; i >>= 1, v |= v >> 1) if(i & 1) r ^= v".
+// Bit k of i flips the top k + 1 bits of r, so bit 31 - j of the result flips parity(i >> j) times: a suffix-XOR scan
+// (five shift-xor steps) and one bit reversal instead of up to 32 loop trips (pinned against the loop in tests/test_pt_cpu.py).
+Y4_HD uint32_t y4_brev32(uint32_t x)
+{
+#if defined(__CUDA_ARCH__)
+	return __brev(x);
+#else
+	x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1); x = ((x >> 2) & 0x33333333u) | ((x & 0x33333333u) << 2);
+	x = ((x >> 4) & 0x0f0f0f0fu) | ((x & 0x0f0f0f0fu) << 4); x = ((x >> 8) & 0x00ff00ffu) | ((x & 0x00ff00ffu) << 8);
+	return (x >> 16) | (x << 16);
+#endif
+}
 Y4_HD float y4_ri_lp(uint32_t i, uint32_t r)
 {
-	for(uint32_t v = 1u << 31; i; i >>= 1, v |= v >> 1)
-		if(i & 1u) r ^= v;
+	i ^= i >> 1; i ^= i >> 2; i ^= i >> 4; i ^= i >> 8; i ^= i >> 16;
+	r ^= y4_brev32(i);
 	return y4_clamp01((float) ((double) r * (double) Y4_2M32));
 }
 Y4_HD uint32_t y4_fnv32a(uint32_t value)
