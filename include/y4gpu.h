@@ -211,7 +211,8 @@ typedef struct y4gpu_pt_layer     /* one `layer` node together with the `texture
 /* pointlight (light_point.cc), arealight (light_area.cc), directional (light_directional.cc), sunlight (light_sun.cc),
    spherelight (light_sphere.cc; light sampling only, like the reference: canIntersect() is false),
    spotlight without soft_shadows (light_spot.cc: a dirac light with a smoothstep cone) */
-enum { Y4GPU_LIGHT_POINT = 0, Y4GPU_LIGHT_AREA = 1, Y4GPU_LIGHT_DIRECTIONAL = 2, Y4GPU_LIGHT_SUN = 3, Y4GPU_LIGHT_SPHERE = 4, Y4GPU_LIGHT_SPOT = 5 };
+enum { Y4GPU_LIGHT_POINT = 0, Y4GPU_LIGHT_AREA = 1, Y4GPU_LIGHT_DIRECTIONAL = 2, Y4GPU_LIGHT_SUN = 3, Y4GPU_LIGHT_SPHERE = 4, Y4GPU_LIGHT_SPOT = 5,
+       Y4GPU_LIGHT_OBJECT = 6 };   /* `objectlight` / `meshlight` (light_object_light.cc): the triangles of a mesh emit */
 typedef struct y4gpu_pt_light
 {
 	int32_t type;                 /* Y4GPU_LIGHT_* ; lights in the reference's (name-sorted) order */
@@ -225,6 +226,9 @@ typedef struct y4gpu_pt_light
 	float angle;                  /* sunlight `angle` (default 0.27) / spotlight `cone_angle` (default 45), degrees */
 	int32_t infinite;             /* directional `infinite` (default 1) */
 	float blend;                  /* spotlight `blend` (default 0.15) */
+	int32_t double_sided;         /* objectlight `double_sided` (default 0) */
+	uint32_t object_n_tris;       /* objectlight: number of triangles of the mesh named by `object_name` */
+	const float *object_tris;     /* objectlight: their world-space vertices [object_n_tris * 9], in the mesh's face order (host memory, copied) */
 } y4gpu_pt_light;
 
 enum { Y4GPU_CAM_PERSPECTIVE = 0, Y4GPU_CAM_ARCHITECT = 1, Y4GPU_CAM_ORTHOGRAPHIC = 2, Y4GPU_CAM_EQUIRECTANGULAR = 3 };

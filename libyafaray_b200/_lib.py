@@ -65,7 +65,8 @@ class PtLayer(C.Structure):
 class PtLight(C.Structure):
     _fields_ = [("type", C.c_int32), ("from_", C.c_float * 3), ("point1", C.c_float * 3), ("point2", C.c_float * 3),
                 ("color", C.c_float * 3), ("power", C.c_float), ("samples", C.c_int32), ("cast_shadows", C.c_int32),
-                ("radius", C.c_float), ("angle", C.c_float), ("infinite", C.c_int32), ("blend", C.c_float)]  # fmt: skip
+                ("radius", C.c_float), ("angle", C.c_float), ("infinite", C.c_int32), ("blend", C.c_float),
+                ("double_sided", C.c_int32), ("object_n_tris", C.c_uint32), ("object_tris", C.c_void_p)]  # fmt: skip
 
 
 class PtCamera(C.Structure):
@@ -102,7 +103,7 @@ class PtAaNoise(C.Structure):
 
 
 MAT_SHINYDIFFUSE, MAT_LIGHT, MAT_MIRROR = 0, 1, 2
-LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT = 0, 1, 2, 3, 4, 5
+LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT, LIGHT_OBJECT = 0, 1, 2, 3, 4, 5, 6
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
 CAMERA_TYPES = {"perspective": 0, "architect": 1, "orthographic": 2, "equirectangular": 3}
 BOKEH_TYPES = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}

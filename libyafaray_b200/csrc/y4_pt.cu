@@ -14,6 +14,7 @@ struct Y4Pt
 {
 	Y4PtScene h_scene;                 // passed to every kernel by value (device pointers inside)
 	std::vector<Y4PtLight> h_lights;   // host copy of the derived lights
+	std::vector<char *> light_blobs;   // device memory owned by object lights (their mesh copy + cdf)
 	Y4PtLight *d_lights = nullptr;
 	Y4PtMaterial *d_mats = nullptr;
 	float4 *d_tri_shade = nullptr;
@@ -261,6 +262,8 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	}
 	for(int l = 1; l < kMaxLanes; ++l) if(pt->lanes[l].stream) cudaStreamDestroy(pt->lanes[l].stream);
 	if(pt->ev_fork) cudaEventDestroy(pt->ev_fork);
+	for(char *b : pt->light_blobs) cudaFree(b);
+	pt->light_blobs.clear();
 	cudaFree(pt->d_mat_transp); cudaFree(pt->d_lights); cudaFree(pt->d_mats); cudaFree(pt->d_normals); cudaFree(pt->d_tri_shade);
 	pt_free_textures(pt);
 	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime); cudaFree(pt->d_sigma_d); cudaFree(pt->d_magic);
@@ -356,7 +359,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		if(mats[i].layer_count < 0 || (mats[i].layer_count > 0 && (mats[i].layer_first < 0 || !ctx->pt || (uint32_t) (mats[i].layer_first + mats[i].layer_count) > ctx->pt->n_layers)))
 		{ ctx->err = "material refers to layers that were not set (call y4gpu_pt_set_textures first)"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_light; ++i)
-		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_SPOT) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
+		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_OBJECT) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	if(!ctx->pt) ctx->pt = new Y4Pt;
 	if(const char *e = getenv("Y4GPU_PT_MIN_BLOCKS")) ctx->pt->stage_min_blocks = atoi(e);
@@ -404,9 +407,29 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	sc.n_lights = (int) n_light; sc.n_mats = (int) n_mat;
 	pt->max_light_samples = 1;
 	pt->h_lights.resize(n_light);
+	for(char *b : pt->light_blobs) cudaFree(b);
+	pt->light_blobs.clear();
 	for(uint32_t i = 0; i < n_light; ++i)
 	{
 		pt->h_lights[i] = derive_light(lights[i]);
+		if(lights[i].type == Y4GPU_LIGHT_OBJECT)
+		{
+			// the light's own copy of its mesh: vertices, geometric normals, area cdf (ObjectLight::initIs) in one device block
+			const uint32_t n = lights[i].object_n_tris;
+			if(!n || !lights[i].object_tris) { ctx->err = "objectlight without triangles"; return Y4GPU_ERR_ARG; }
+			std::vector<float> cdf; std::vector<float4> ng;
+			derive_object_light(pt->h_lights[i], lights[i].object_tris, n, cdf, ng);
+			char *blob = nullptr;
+			Y4_CUDA(ctx, cudaMalloc(&blob, (size_t) n * (16 + 36 + 4)));
+			pt->light_blobs.push_back(blob);
+			Y4_CUDA(ctx, cudaMemcpyAsync(blob, ng.data(), (size_t) n * 16, cudaMemcpyHostToDevice, st));
+			Y4_CUDA(ctx, cudaMemcpyAsync(blob + (size_t) n * 16, lights[i].object_tris, (size_t) n * 36, cudaMemcpyHostToDevice, st));
+			Y4_CUDA(ctx, cudaMemcpyAsync(blob + (size_t) n * 52, cdf.data(), (size_t) n * 4, cudaMemcpyHostToDevice, st));
+			Y4_CUDA(ctx, cudaStreamSynchronize(st));
+			pt->h_lights[i].obj_ng = reinterpret_cast<const float4 *>(blob);
+			pt->h_lights[i].obj_tris = reinterpret_cast<const float *>(blob + (size_t) n * 16);
+			pt->h_lights[i].obj_cdf = reinterpret_cast<const float *>(blob + (size_t) n * 52);
+		}
 		const int ns = y4_light_num_samples(sc, pt->h_lights[i]);
 		if(ns > pt->max_light_samples) pt->max_light_samples = ns;
 	}

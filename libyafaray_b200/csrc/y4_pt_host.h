@@ -219,9 +219,15 @@ inline Y4PtLight derive_light(const y4gpu_pt_light &l)
 		o.sq_radius_eps = (float) ((double) o.sq_radius * 1.000003815);
 		return o;
 	}
+	const float pi_f = (float) 3.14159265358979323846264338327950288L;
+	if(l.type == Y4GPU_LIGHT_OBJECT)                      // ObjectLight::factory: color * (float) power * num_pi; area / cdf: derive_object_light
+	{
+		o.color = c3(pi_f * (l.power * l.color[0]), pi_f * (l.power * l.color[1]), pi_f * (l.power * l.color[2]));
+		o.double_sided = l.double_sided; o.obj_n = (int) l.object_n_tris;
+		return o;
+	}
 	const HV corner = hv(l.from), to_x = hv(l.point1) - corner, to_y = hv(l.point2) - corner;
 	HV fnormal = to_y ^ to_x;
-	const float pi_f = (float) 3.14159265358979323846264338327950288L;
 	o.color = c3(pi_f * (l.power * l.color[0]), pi_f * (l.power * l.color[1]), pi_f * (l.power * l.color[2]));   // col * inte * num_pi
 	// area_ = fnormal_.normLen(): normalises fnormal_ and returns its former length (vector.h)
 	float len = lensqr(fnormal);
@@ -238,6 +244,32 @@ inline Y4PtLight derive_light(const y4gpu_pt_light &l)
 	o.to_x = tov(to_x); o.to_y = tov(to_y);
 	o.c2 = tov(corner + to_x); o.c3 = tov(corner + (to_x + to_y)); o.c4 = tov(corner + to_y);
 	return o;
+}
+
+// ObjectLight::initIs (light_object_light.cc:46-70): triangle areas (TrianglePrimitive::surfaceArea, primitive_triangle.cc:208-213),
+// their sum in double, Pdf1D::cumulateStep1DDf (sample_pdf1d.h:67-82) and the geometric normals.  Fills area / inv_area of `o`;
+// the caller stores the three arrays where the light's pointers can reach them.
+inline void derive_object_light(Y4PtLight &o, const float *tris, uint32_t n, std::vector<float> &cdf, std::vector<float4> &ng)
+{
+	cdf.assign(n, 0.f); ng.resize(n);
+	std::vector<float> areas(n);
+	double total_area = 0.0;
+	for(uint32_t i = 0; i < n; ++i)
+	{
+		const float *v = tris + 9ull * i;
+		const HV a = {v[0], v[1], v[2]}, b = {v[3], v[4], v[5]}, c = {v[6], v[7], v[8]};
+		const HV cr = (b - a) ^ (c - a);
+		areas[i] = 0.5f * sqrtf(lensqr(cr));
+		total_area += areas[i];
+		ng[i] = y4_tri_shade(tris, nullptr, 1u, i);
+	}
+	const double delta = 1.0 / (double) n;
+	double acc = 0.0;
+	for(uint32_t i = 0; i < n; ++i) { acc += (double) areas[i] * delta; cdf[i] = (float) acc; }
+	const float integral = (float) acc;
+	for(uint32_t i = 0; i < n; ++i) cdf[i] /= integral;
+	o.area = (float) total_area;
+	o.inv_area = (float) (1.f / total_area);
 }
 
 // ImageFilm ctor: filter table, filter width, table scale (imagefilm.cc:129-173, math/filter.h:34-90)

@@ -15,6 +15,7 @@
 //                                              src/integrator/surface/integrator_montecarlo.cc:80-383
 #pragma once
 #include "y4_pt_types.cuh"
+#include "y4_tri.cuh"
 
 // ---- surface ---------------------------------------------------------------------------------
 // Per-triangle shading record, computed once per scene: the face normal of calculateNormal
@@ -348,6 +349,46 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 		ls.dir = ldir; ls.tmax = dist; ls.col = L.color;
 		return true;
 	}
+	if(L.type == Y4GPU_LIGHT_OBJECT)
+	{
+		// ObjectLight::sampleSurface (light_object_light.cc:87-105): Pdf1D::dSample = lower_bound on the cdf, the sample number
+		// re-stretched inside the chosen triangle's cdf step, TrianglePrimitive::sample (primitive_triangle.cc:228-234)
+		const int n = L.obj_n;
+		int idx;
+		if(s1 <= 0.f) idx = 0;
+		else if(s1 >= 1.f) idx = n - 1;
+		else
+		{
+			int lo = 0, hi = n;                               // first index with cdf[idx] >= s1
+			while(lo < hi) { const int mid = (lo + hi) >> 1; if(L.obj_cdf[mid] < s1) lo = mid + 1; else hi = mid; }
+			idx = lo;
+		}
+		if(idx >= n) return false;                            // "Sampling error": a null point and normal -> no light
+		float delta = L.obj_cdf[idx], ss1;
+		if(idx > 0) { const float below = L.obj_cdf[idx - 1]; delta = xsub(delta, below); ss1 = xdiv(xsub(s1, below), delta); }
+		else ss1 = xdiv(s1, delta);
+		const float *tv = L.obj_tris + 9ull * (uint32_t) idx;
+		const float su1 = xsqrt(ss1), u = xsub(1.f, su1), v = xmul(s2, su1), w = xsub(xsub(1.f, u), v);
+		const V3 p = xadd3(xadd3(xscale(v3(tv[0], tv[1], tv[2]), u), xscale(v3(tv[3], tv[4], tv[5]), v)), xscale(v3(tv[6], tv[7], tv[8]), w));
+		const float4 ng4 = L.obj_ng[idx];
+		const V3 nl = v3(ng4.x, ng4.y, ng4.z);
+		// illumSample (:109-146)
+		V3 ldir = xsub3(p, from);
+		const float dist_sqr = xdot(ldir, ldir);
+		const float dist = xsqrt(dist_sqr);
+		if(dist <= 0.f) return false;
+		ldir = xscale(ldir, xdiv(1.f, dist));
+		float cos_angle = -xdot(ldir, nl);
+		if(cos_angle <= 0.f)
+		{
+			if(L.double_sided) cos_angle = -cos_angle;
+			else return false;
+		}
+		const float amc = xmul(L.area, cos_angle);
+		ls.pdf = (float) (xdmul((Y4_WIDE) dist_sqr, Y4_PI) / (Y4_WIDE) (amc == 0.f ? 1e-8f : amc));
+		ls.dir = ldir; ls.tmax = dist; ls.col = L.color;
+		return true;
+	}
 	if(L.type == Y4GPU_LIGHT_SUN)
 	{
 		ls.dir = y4_sample_cone(L.dir, L.du, L.dv, L.cos_angle, s1, s2);
@@ -373,9 +414,35 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 	return true;
 }
 
-// Light::intersect of the lights with canIntersect(): AreaLight (light_area.cc:117-151), SunLight (light_sun.cc:70-78)
-Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, float &t, C3 &col, float &ipdf)
+// Light::intersect of the lights with canIntersect(): AreaLight (light_area.cc:117-151), SunLight (light_sun.cc:70-78), ObjectLight
+Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, float tmin, float &t, C3 &col, float &ipdf)
 {
+	if(L.type == Y4GPU_LIGHT_OBJECT)
+	{
+		// ObjectLight::intersect (:183-201): closest hit of the light's own accelerator over [ray.tmin_, inf) -- here a loop over its
+		// triangles with the accelerator's triangle test and tie rule.  The reference never writes its `t` argument: the caller's
+		// b_ray.tmax_ keeps its initial -1, so 1 / (t * t) is 1 and the shadow ray that follows is unbounded.  Reproduced.
+		int best = -1; float best_t = 0.f;
+		for(int k = 0; k < L.obj_n; ++k)
+		{
+			const Y4Tri tr = y4_tri_setup(L.obj_tris + 9ull * (uint32_t) k, (uint32_t) k, 0u);
+			float tt, uu, vv;
+			if(!y4_tri_intersect(from, dir, v3(tr.v0x, tr.v0y, tr.v0z), v3(tr.e1x, tr.e1y, tr.e1z), v3(tr.e2x, tr.e2y, tr.e2z), tr.eps, tt, uu, vv)) continue;
+			if(!(tt >= tmin)) continue;
+			if(best < 0 || tt < best_t) { best = k; best_t = tt; }
+		}
+		if(best < 0) return false;
+		const float4 ng4 = L.obj_ng[best];
+		float cos_angle = -xdot(dir, v3(ng4.x, ng4.y, ng4.z));                // ray.dir_ * (-n)
+		if(cos_angle <= 0.f)
+		{
+			if(L.double_sided) cos_angle = fabsf(cos_angle);
+			else return false;
+		}
+		ipdf = (float) xdmul((Y4_WIDE) xmul(xmul(1.f, L.area), cos_angle), Y4_1_PI);
+		col = L.color; t = -1.f;
+		return true;
+	}
 	if(L.type == Y4GPU_LIGHT_SUN)
 	{
 		const float cosine = xdot(dir, L.dir);
@@ -460,7 +527,7 @@ Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtM
 		const uint32_t fl = Y4_BSDF_GLOSSY | Y4_BSDF_DIFFUSE | Y4_BSDF_DISPERSIVE | Y4_BSDF_REFLECT | Y4_BSDF_TRANSMIT;
 		const C3 surf = y4_mat_sample(m, sp, wo, s1, s2, fl, wi, W, s_pdf, sampled, specular);
 		float t = 0.f, ipdf = 0.f; C3 lcol = c3f(0.f);
-		if(s_pdf > 1e-6f && y4_light_intersect(L, sp.p, wi, t, lcol, ipdf) && ipdf > 1e-6f)
+		if(s_pdf > 1e-6f && y4_light_intersect(L, sp.p, wi, tmin_b, t, lcol, ipdf) && ipdf > 1e-6f)
 		{
 			const float l_pdf = xdiv(1.f, ipdf);
 			const float l2 = xmul(l_pdf, l_pdf), m2 = xmul(s_pdf, s_pdf);

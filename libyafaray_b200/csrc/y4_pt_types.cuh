@@ -93,10 +93,15 @@ struct Y4PtLight
 	float cos_start, cos_end, icos_diff;   // spot (light_spot.cc:30-43); its ndir_ is kept in `dir`
 	float radius, sq_radius, sq_radius_eps;
 	int infinite;
+	// objectlight (light_object_light.cc): the mesh's triangles, geometric normals and the area distribution's cdf
+	int double_sided, obj_n;
+	const float *obj_tris;      // [obj_n * 9] world-space vertices
+	const float4 *obj_ng;       // [obj_n] Primitive::getGeometricNormal
+	const float *obj_cdf;       // [obj_n] Pdf1D::cdf_ of the triangle areas
 };
 // Light::diracLight() / Light::canIntersect() of the supported lights (include/light/light_*.h)
 Y4_HD bool y4_light_dirac(int type) { return type == Y4GPU_LIGHT_POINT || type == Y4GPU_LIGHT_DIRECTIONAL || type == Y4GPU_LIGHT_SPOT; }
-Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN; }
+Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN || type == Y4GPU_LIGHT_OBJECT; }
 
 #define Y4_PT_MAX_LIGHTS 64
 #define Y4_FILTER_TABLE 16

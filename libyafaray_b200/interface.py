@@ -222,7 +222,7 @@ class Interface:
 
     def createLight(self, name):
         p = dict(self.params)
-        if p.get("type") not in ("pointlight", "arealight", "directional", "sunlight", "spherelight", "spotlight"):
+        if p.get("type") not in ("pointlight", "arealight", "directional", "sunlight", "spherelight", "spotlight", "objectlight", "meshlight"):
             raise Y4Error(f"light type '{p.get('type')}' is not supported by the GPU back end")
         if p.get("type") == "spotlight" and p.get("soft_shadows", False):
             raise Y4Error("spotlight soft_shadows is not supported by the GPU back end")
@@ -532,6 +532,7 @@ class Interface:
         wanted = [s for s in str(view.get("light_names", "")).split(";") if s]
         light_names = [n for n in sorted(self.lights) if self.lights[n].get("light_enabled", True) and (not wanted or n in wanted)]
         lights = (_lib.PtLight * max(1, len(light_names)))()
+        self._light_tris = []
         for i, n in enumerate(light_names):
             p, l = self.lights[n], lights[i]
             if p.get("photon_only", False):
@@ -555,6 +556,14 @@ class Interface:
                 l.type, l.angle, l.blend = _lib.LIGHT_SPOT, float(p.get("cone_angle", 45.0)), float(p.get("blend", 0.15))
                 l.from_[:] = p.get("from", (0.0, 0.0, 0.0))
                 l.point1[:] = p.get("to", (0.0, 0.0, -1.0))
+            elif p["type"] in ("objectlight", "meshlight"):     # ObjectLight::factory (light_object_light.cc:222-253)
+                o = self.objects.get(str(p.get("object_name", "")))
+                if o is None or o.instance_of or not o.tris:
+                    raise Y4Error(f"objectlight '{n}': object_name must name a mesh with triangles")
+                ov = np.asarray(o.verts, np.float64).astype(np.float32)[np.asarray(o.tris, np.int64)].reshape(-1, 9)
+                self._light_tris.append(np.ascontiguousarray(ov))          # kept alive until the scene is uploaded
+                l.type, l.samples, l.double_sided = _lib.LIGHT_OBJECT, int(p.get("samples", 4)), int(p.get("double_sided", False))
+                l.object_n_tris, l.object_tris = len(ov), self._light_tris[-1].ctypes.data
             elif p["type"] == "spherelight":       # SphereLight::factory (light_sphere.cc:160-195)
                 l.type, l.samples, l.radius = _lib.LIGHT_SPHERE, int(p.get("samples", 4)), float(p.get("radius", 1.0))
                 l.from_[:] = p.get("from", (0.0, 0.0, 0.0))
@@ -609,7 +618,8 @@ class Interface:
         pr.profile = int(rp.get("b200_profile", 0))
         tri_orco = np.ascontiguousarray(np.concatenate(orcos), np.float32) if layer_list and orcos else None
         tri_uv = np.ascontiguousarray(np.concatenate(uvs), np.float32) if layer_list and uvs else None
-        return {"tris": T, "flags": F, "normals": N, "cam": cam, "mats": mats, "n_mat": len(mat_names), "lights": lights,
+        return {"_light_tris": self._light_tris,      # the object lights' vertex arrays the `lights` structs point into
+                "tris": T, "flags": F, "normals": N, "cam": cam, "mats": mats, "n_mat": len(mat_names), "lights": lights,
                 "n_light": len(light_names), "params": pr, "textures": textures, "n_tex": len(tex_list), "layers": layers,
                 "n_layers": len(layer_list), "tri_orco": tri_orco, "tri_uv": tri_uv, "_texels": texel_arrays}
 

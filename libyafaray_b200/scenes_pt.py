@@ -84,7 +84,7 @@ def _uv_sphere(centre, radius, nu, nv):
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
                 oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None,
-                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None):
+                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None, mesh_light=None):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front.
     mirror: {"objects": subset of ("tall", "short", "back", "left", "sphere"), "color": rgb, "reflect": r} -> those objects get a
@@ -135,6 +135,9 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         v, t = _uv_sphere((0.33, 0.42, 0.35), 0.12, 12, 7)
         _mesh(api, "i_sphere", mat("sphere", "white"), v, t)
         api.smoothMesh("i_sphere", float(smooth_sphere))
+    if mesh_light and mesh_light.get("shape") == "sphere":      # a small emitting sphere that an objectlight turns into a light source
+        v, t = _uv_sphere((0.3, 0.7, 0.35), 0.07, 8, 5)
+        _mesh(api, "k_bulb", "emitter", v, t)
     if pane:
         v, t = _quad((0.1, 0.05, 0.45), (0.9, 0.05, 0.45), (0.9, 0.8, 0.45), (0.1, 0.8, 0.45))
         _mesh(api, "j_pane", "pane", v, t)
@@ -146,6 +149,13 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         api.paramsSetVector("from", 0.5, 0.9, 0.5)
         api.paramsSetColor("color", 1.0, 0.85, 0.6, 1.0)
         api.paramsSetFloat("power", 0.6)
+    elif mesh_light:                                    # objectlight on the lamp quad (2 triangles) or on the bulb sphere
+        api.paramsSetString("type", "objectlight")
+        api.paramsSetString("object_name", "k_bulb" if mesh_light.get("shape") == "sphere" else "h_lamp")
+        api.paramsSetColor("color", 1.0, 0.85, 0.6, 1.0)
+        api.paramsSetFloat("power", float(mesh_light.get("power", 18.0)))
+        api.paramsSetInt("samples", light_samples)
+        api.paramsSetBool("double_sided", bool(mesh_light.get("double_sided", False)))
     else:
         api.paramsSetString("type", "arealight")
         api.paramsSetVector("corner", lx0, ly, lz0)

@@ -139,7 +139,15 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	sc.n_lights = (int) n_light; sc.n_mats = (int) n_mat;
 	int max_ls = 1;
 	std::vector<Y4PtLight> hl(n_light);
-	for(uint32_t i = 0; i < n_light; ++i) { hl[i] = derive_light(lights[i]); const int ns = y4_light_num_samples(sc, hl[i]); if(ns > max_ls) max_ls = ns; }
+	static std::vector<std::vector<float>> obj_cdf, obj_tris; static std::vector<std::vector<float4>> obj_ng;     // object lights' mesh copies
+	obj_cdf.assign(n_light, {}); obj_tris.assign(n_light, {}); obj_ng.assign(n_light, {});
+	for(uint32_t i = 0; i < n_light; ++i) { hl[i] = derive_light(lights[i]);
+		if(lights[i].type == Y4GPU_LIGHT_OBJECT)
+		{
+			obj_tris[i].assign(lights[i].object_tris, lights[i].object_tris + 9ull * lights[i].object_n_tris);
+			derive_object_light(hl[i], obj_tris[i].data(), lights[i].object_n_tris, obj_cdf[i], obj_ng[i]);
+			hl[i].obj_tris = obj_tris[i].data(); hl[i].obj_cdf = obj_cdf[i].data(); hl[i].obj_ng = obj_ng[i].data();
+		} const int ns = y4_light_num_samples(sc, hl[i]); if(ns > max_ls) max_ls = ns; }
 	std::vector<float4> tri_shade(n_tri);
 	for(int t = 0; t < n_tri; ++t) tri_shade[t] = y4_tri_shade(verts, flags, n_mat, (uint64_t) t);
 	std::vector<Y4PtMaterial> hm(n_mat);

@@ -63,6 +63,10 @@ PT_GOLDEN_DOF = {
 
 # directional (infinite + finite beam), sunlight and spherelight next to the ceiling area light -> pt_lights.npz
 PT_GOLDEN_LIGHTS = {
+    # objectlight / meshlight: an emitting sphere mesh (70 triangles) sampled through the area cdf, single-light path tracing (sample-exact)
+    "mesh_light_sphere": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, light_samples=2, mesh_light=dict(shape="sphere", power=40.0)),
+    "mesh_light_quad_double_sided_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", light_samples=3,
+                                                mesh_light=dict(double_sided=True)),
     "six_lights": dict(scene="cornell", width=64, height=36, spp=3, bounces=3, light_samples=2,
                         extra_lights=("sun", "directional", "directional_finite", "sphere", "spot")),
     "sun_sphere_spot_direct": dict(scene="cornell", width=64, height=36, spp=2, bounces=2, integrator="directlighting", light_samples=3,

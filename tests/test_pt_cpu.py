@@ -355,6 +355,26 @@ def test_shinydiffuse_translucency_vs_live_reference(variant):
     assert helpers.psnr(interface.normalize_film(w, rgba), ref) >= 100.0
 
 
+MESH_LIGHTS = [dict(mesh_light=dict(), light_samples=3, path_samples=2),
+               dict(mesh_light=dict(shape="sphere", power=40.0, double_sided=True), integrator="directlighting", light_samples=4),
+               dict(mesh_light=dict(shape="sphere", power=30.0), extra_lights=("spot",), light_samples=2)]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("variant", MESH_LIGHTS)
+def test_object_light_vs_live_reference(variant):
+    """objectlight / meshlight (light_object_light.cc): triangle areas, their Pdf1D cdf, dSample + TrianglePrimitive::sample in
+    illumSample, and intersect -- including the reference never writing its `t` argument, which makes the MIS weight of the
+    material sample distance-free and its shadow ray unbounded."""
+    kw = dict(width=64, height=36, spp=3, bounces=3, **variant)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    a = _assemble(**kw)
+    w, rgba = helpers.emu_pt_render(a, ref_light_order=a["n_light"] > 1 and a["params"].path_samples > 0)
+    assert helpers.psnr(interface.normalize_film(w, rgba), ref) >= 100.0
+
+
 def test_transparency_combinations_outside_the_chain_model_are_rejected():
     """reflection + refraction at one vertex (two child rays) is refused."""
     yi = interface.Interface()
