@@ -127,7 +127,7 @@ def test_interface_rejects_unsupported_features():
     with pytest.raises(Y4Error):
         yi.createCamera("c")
     yi.paramsClearAll()
-    yi.paramsSetString("type", "meshlight")
+    yi.paramsSetString("type", "bglight")
     with pytest.raises(Y4Error):
         yi.createLight("l")
     yi.paramsClearAll()
