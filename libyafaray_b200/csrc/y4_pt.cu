@@ -394,7 +394,12 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 			if(params->transp_shadows && mats[m].layer_count > 0) { ctx->err = "textured transparent materials with transpShad are not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 		}
 	// no_recursive makes a mirror hit start sub-paths AND recurse: two branches per vertex, which the linear ray-level chain does not cover
-	if(sc.has_specular && sc.no_recursive) { ctx->err = "no_recursive with mirror materials / specular_reflect is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
+	bool chain_mats = false;
+	for(uint32_t m = 0; m < n_mat; ++m)
+		chain_mats = chain_mats || mats[m].type == Y4GPU_MAT_MIRROR || (mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f));
+	if(chain_mats && sc.no_recursive) { ctx->err = "no_recursive with mirror materials / specular_reflect is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
+	// object lights need the general kernel variant as well (not the ray levels)
+	for(uint32_t l = 0; l < n_light; ++l) if(lights[l].type == Y4GPU_LIGHT_OBJECT && !sc.has_specular) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;

@@ -332,6 +332,9 @@ Y4_HD bool y4_light_illuminate(const Y4PtLight &L, const V3 p, Y4LSample &ls)
 
 // Light::illumSample of the sampled lights: AreaLight (light_area.cc:66-96), SunLight (light_sun.cc:54-68),
 // SphereLight (light_sphere.cc:69-98)
+// GENERAL = false: the kernel variant for scenes without specular materials and object lights (see y4_vertex); the object
+// light's code folds away there
+template<bool GENERAL = true>
 Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, float s2, Y4LSample &ls)
 {
 	if(L.type == Y4GPU_LIGHT_AREA)
@@ -349,7 +352,7 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 		ls.dir = ldir; ls.tmax = dist; ls.col = L.color;
 		return true;
 	}
-	if(L.type == Y4GPU_LIGHT_OBJECT)
+	if(GENERAL && L.type == Y4GPU_LIGHT_OBJECT)
 	{
 		// ObjectLight::sampleSurface (light_object_light.cc:87-105): Pdf1D::dSample = lower_bound on the cdf, the sample number
 		// re-stretched inside the chosen triangle's cdf step, TrianglePrimitive::sample (primitive_triangle.cc:228-234)
@@ -415,9 +418,10 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 }
 
 // Light::intersect of the lights with canIntersect(): AreaLight (light_area.cc:117-151), SunLight (light_sun.cc:70-78), ObjectLight
+template<bool GENERAL = true>
 Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, float tmin, float &t, C3 &col, float &ipdf)
 {
-	if(L.type == Y4GPU_LIGHT_OBJECT)
+	if(GENERAL && L.type == Y4GPU_LIGHT_OBJECT)
 	{
 		// ObjectLight::intersect (:183-201): closest hit of the light's own accelerator over [ray.tmin_, inf) -- here a loop over its
 		// triangles with the accelerator's triangle test and tie rule.  The reference never writes its `t` argument: the caller's
@@ -478,6 +482,7 @@ Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, f
 	return true;
 }
 
+template<bool GENERAL = true>
 Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo,
                             float s1, float s2, Y4DirectOut &out)
 {
@@ -500,7 +505,7 @@ Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtM
 	}
 	const bool can_intersect = y4_light_can_intersect(L.type);
 	// ---- areaLightSampleLight ----
-	if(y4_light_illum_sample(L, sp.p, s1, s2, ls) && ls.pdf > 1e-6f)
+	if(y4_light_illum_sample<GENERAL>(L, sp.p, s1, s2, ls) && ls.pdf > 1e-6f)
 	{
 		const C3 surf = y4_mat_eval(m, sp, wo, ls.dir);
 		const float angle = m.flat_material ? 1.f : fabsf(xdot(sp.n, ls.dir));
@@ -527,7 +532,7 @@ Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtM
 		const uint32_t fl = Y4_BSDF_GLOSSY | Y4_BSDF_DIFFUSE | Y4_BSDF_DISPERSIVE | Y4_BSDF_REFLECT | Y4_BSDF_TRANSMIT;
 		const C3 surf = y4_mat_sample(m, sp, wo, s1, s2, fl, wi, W, s_pdf, sampled, specular);
 		float t = 0.f, ipdf = 0.f; C3 lcol = c3f(0.f);
-		if(s_pdf > 1e-6f && y4_light_intersect(L, sp.p, wi, tmin_b, t, lcol, ipdf) && ipdf > 1e-6f)
+		if(s_pdf > 1e-6f && y4_light_intersect<GENERAL>(L, sp.p, wi, tmin_b, t, lcol, ipdf) && ipdf > 1e-6f)
 		{
 			const float l_pdf = xdiv(1.f, ipdf);
 			const float l2 = xmul(l_pdf, l_pdf), m2 = xmul(s_pdf, s_pdf);

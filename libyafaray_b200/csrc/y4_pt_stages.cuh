@@ -343,6 +343,7 @@ Y4_HD void y4_light_sample_numbers(const Y4PtScene &sc, const Y4PtWave &W, const
 // all_lights: vertex = camera hit (estimateAllDirectLight, light index given);
 // otherwise : vertex = current path vertex, light = W.lnum[i] (estimateOneDirectLight).
 // Returns the mask of shadow-ray slots written (bit q -> W.sray[q * n + i]).
+template<bool SPEC = true>
 Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, uint32_t &f, bool all_lights, int light, int k, const Y4Vertex &vx, float4 cache)
 {
 	const uint32_t n = W.n;
@@ -353,7 +354,7 @@ Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 	float s1 = 0.f, s2 = 0.f;
 	if(!y4_light_dirac(L.type)) y4_light_sample_numbers(sc, W, ps, i, l, k, num_samples, cache, s1, s2);
 	Y4DirectOut out;
-	y4_direct_sample(sc, L, vx.m, vx.sp, vx.wo, s1, s2, out);
+	y4_direct_sample<SPEC>(sc, L, vx.m, vx.sp, vx.wo, s1, s2, out);
 	const bool cast = L.cast_shadows && vx.m.receive_shadows;
 	uint32_t mask = 0u;
 	for(int q = 0; q < 2; ++q)
@@ -537,7 +538,7 @@ Y4_HD uint32_t y4_stage_primary(const Y4PtScene &sc, const Y4PtWave &W, const Y4
 	const int what = y4_pt_primary<SPEC>(sc, W, i, level, f, vx);
 	if(what == 1)
 	{
-		if(l0 >= 0) push |= y4_pt_direct(sc, W, ps, i, f, true, l0, 0, vx, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
+		if(l0 >= 0) push |= y4_pt_direct<SPEC>(sc, W, ps, i, f, true, l0, 0, vx, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
 		if(f & (Y4_PF_DIRECT | Y4_PF_PATHS | Y4_PF_RECURSE)) push |= Y4_PUSH_PATH;
 	}
 	else if(what == 2) push |= Y4_PUSH_SPEC;
@@ -558,7 +559,7 @@ Y4_HD uint32_t y4_stage_direct_step(const Y4PtScene &sc, const Y4PtWave &W, cons
 	{
 		const Y4Ray r = all_lights ? y4_level_ray<SPEC>(sc, W, ps, i, f, W.pix[i], W.samp[i]) : ld_ray(W.ray, i);
 		const Y4Vertex vx = y4_vertex<SPEC>(sc, r, all_lights ? ld_hit(W.hit0, i) : ld_hit(W.hit, i));
-		push = y4_pt_direct(sc, W, ps, i, f, all_lights, l, k, vx, cache);
+		push = y4_pt_direct<SPEC>(sc, W, ps, i, f, all_lights, l, k, vx, cache);
 	}
 	W.flags[i] = f;
 	return push;
@@ -620,7 +621,7 @@ Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtP
 		if(!cblack(emit)) { st3(W.lcol, i, emit); f |= Y4_PF_LCOL; } else f &= ~(uint32_t) Y4_PF_LCOL;
 		st3(W.pthr, i, thr);
 		f |= Y4_PF_DIRECT;
-		push |= y4_pt_direct(sc, W, ps, i, f, false, -1, 0, vx, cache);
+		push |= y4_pt_direct<SPEC>(sc, W, ps, i, f, false, -1, 0, vx, cache);
 	}
 	else
 	{

@@ -128,6 +128,8 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].translucency > 0.00001f && !sc.has_specular) sc.has_specular = 1;
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f)) sc.has_specular = 2;
 	}
+	// object lights need the general kernel variant as well (not the ray levels)
+	for(uint32_t l = 0; l < n_light; ++l) if(lights[l].type == Y4GPU_LIGHT_OBJECT && !sc.has_specular) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;

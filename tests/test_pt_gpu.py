@@ -20,7 +20,7 @@ ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: 
               **{k: ("pt_mirror.npz", v) for k, v in PT_GOLDEN_MIRROR.items()},
               # several lights + path tracing: light choice numbering differs from the reference's thread-dependent counter
               # (DESIGN.md), those are checked against the CPU emulation below and the emulation against the golden image
-              **{k: ("pt_lights.npz", v) for k, v in PT_GOLDEN_LIGHTS.items() if v.get("integrator") == "directlighting"}}
+              **{k: ("pt_lights.npz", v) for k, v in PT_GOLDEN_LIGHTS.items() if v.get("integrator") == "directlighting" or not v.get("extra_lights")}}
 
 PSNR_MIN = 50.0  # BASELINE.json north_star: PSNR >= 50 dB at equal spp with identical sample sequences
 
