@@ -192,6 +192,9 @@ void launch_stage(int minb, int grid, cudaStream_t st, const Y4PtScene &sc, cons
 	// second instantiation for scenes without specular materials: see y4_vertex
 	if(sc.has_specular || STAGE == kStLevelFinish)
 	{
+		// the general variant carries more live state: its own register budget (env Y4GPU_PT_GENERAL_MIN_BLOCKS, default = the plain one's)
+		static const int general_minb = getenv("Y4GPU_PT_GENERAL_MIN_BLOCKS") ? atoi(getenv("Y4GPU_PT_GENERAL_MIN_BLOCKS")) : 0;
+		if(general_minb >= 2) minb = general_minb;
 		if(minb >= 4) k_pt_stage<STAGE, 4, true><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
 		else if(minb == 3) k_pt_stage<STAGE, 3, true><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
 		else k_pt_stage<STAGE, 2, true><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
