@@ -78,6 +78,8 @@ typedef struct y4gpu_stats
 	uint64_t last_trace_rays;
 	uint64_t nodes_visited, tris_tested; /* filled by y4gpu_trace_counted only */
 	uint64_t kernel_launches;           /* kernels launched by this ctx since creation */
+	uint64_t bvh_levels;                /* depth of the BVH8 of the last build (the traversal stack holds Y4_STACK_SIZE = 64 entries;
+	                                       builds deeper than 56 levels are refused with Y4GPU_ERR_UNSUPPORTED) */
 } y4gpu_stats;
 
 /* lifetime ------------------------------------------------------------------------------ */
@@ -262,13 +264,14 @@ typedef struct y4gpu_pt_params
 	int32_t min_raydist_auto; float min_raydist;        /* adv_auto_min_raydist_enabled / adv_min_raydist_value */
 	uint32_t base_sampling_offset;                      /* adv_base_sampling_offset + 100000 * adv_computer_node */
 	uint32_t rr_seed;             /* seed of the per-path Russian-roulette hash (the reference uses rand()) */
-	uint32_t wave_size;           /* pixel-samples processed per wavefront (0 = default 2^21) */
+	uint32_t wave_size;           /* pixel-samples processed per wavefront (0 = default 2^22) */
 	int32_t profile;              /* 1: time every kernel class with CUDA events and count BVH visits (slower; for the roofline) */
 	int32_t transp_shadows;       /* integrator transpShad: shadow rays take the intersectTs rules (material visibility only,
-	                                 tmin <= t < t_max; accelerator_kdtree.cc:911-1061).  Every supported material is opaque,
-	                                 so a blocker always shadows and the filter colour is exactly 1 */
-	int32_t shadow_depth;         /* integrator shadowDepth (unused while every supported material is opaque) */
-	int32_t raydepth;             /* integrator `raydepth` (default 5): specular recursion levels (integrator_montecarlo.cc:916-964) */
+	                                 tmin <= t < t_max; accelerator_kdtree.cc:911-1061): opaque blockers shadow, transparent
+	                                 shinydiffuse blockers multiply their getTransparency colour into the light sample */
+	int32_t shadow_depth;         /* integrator shadowDepth: distinct transparent blockers a shadow ray may cross (<= 16, else UNSUPPORTED) */
+	int32_t raydepth;             /* integrator `raydepth` (default 5): specular recursion levels (integrator_montecarlo.cc:916-964);
+	                                 <= 19, else UNSUPPORTED */
 	int32_t trace_caustics;       /* caustic_type path / both: emission found after a specular bounce of a path counts
 	                                 (integrator_path_tracer.cc:227,256-264) */
 	int32_t transp_refracted_background;   /* bg_transp_refract (TiledIntegrator::background, integrator_tiled.cc:707-720) */

@@ -33,7 +33,7 @@ class Stats(C.Structure):
         ("build_ms", C.c_double), ("last_trace_ms", C.c_double),
         ("last_trace_rays", C.c_uint64),
         ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
-        ("kernel_launches", C.c_uint64),
+        ("kernel_launches", C.c_uint64), ("bvh_levels", C.c_uint64),
     ]  # fmt: skip
 
 

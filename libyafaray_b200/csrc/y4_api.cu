@@ -65,6 +65,7 @@ int y4gpu_create(int device, y4gpu_ctx **out)
 }
 
 void y4gpu_pt_release(y4gpu_ctx *ctx);   // y4_pt.cu
+} void y4_pt_invalidate(y4gpu_ctx *ctx); extern "C" {
 
 void y4gpu_destroy(y4gpu_ctx *ctx)
 {
@@ -100,6 +101,7 @@ int y4gpu_upload_triangles(y4gpu_ctx *ctx, const float *v_xyz, const uint32_t *f
 	// a re-upload of the same size (animation frame, repeated render) reuses the device arrays
 	const bool reuse = n_tri && n_tri == ctx->n_tri && ctx->d_verts && (!flags == !ctx->d_flags);
 	ctx->built = false;
+	y4_pt_invalidate(ctx);
 	if(!reuse)
 	{
 		cudaFree(ctx->d_verts); cudaFree(ctx->d_flags);
@@ -124,6 +126,7 @@ int y4gpu_build(y4gpu_ctx *ctx, const y4gpu_build_params *params)
 	std::lock_guard<std::mutex> lock(ctx->mtx);
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	int leaf_max = params && params->leaf_max ? params->leaf_max : 1;
+	y4_pt_invalidate(ctx);
 	return y4_build_bvh(ctx, leaf_max);
 }
 
@@ -188,6 +191,7 @@ int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int m
 {
 	if(!ctx || (n && (!rays || !out)) || (n_mat && !mat_transparency) || max_depth < 0) return Y4GPU_ERR_ARG;
 	std::lock_guard<std::mutex> lock(ctx->mtx);
+	if(max_depth > 16) { ctx->err = "y4gpu_trace_tshadow: max_depth > 16 is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(!ctx->built) { ctx->err = "y4gpu_trace_tshadow before y4gpu_build"; return Y4GPU_ERR_ARG; }
 	if(n == 0) return Y4GPU_OK;
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));

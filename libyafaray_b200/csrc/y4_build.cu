@@ -472,8 +472,10 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 		ctx->stats.kernel_launches++;
 		if(++levels > 256) { ctx->err = "collapse did not terminate"; return Y4GPU_ERR_CUDA; }
 	}
-	// the traversal kernels keep at most one pending sibling group per level (+ a few postponed triangle groups, which are
-	// bounded separately) on a Y4_STACK_SIZE-entry stack: refuse a tree they could overflow instead of corrupting memory
+	// the traversal kernels keep at most one pending sibling group per level plus postponed triangle groups, which are only
+	// pushed while sp < Y4_STACK_SIZE - levels (Y4Bvh8::postpone_sp_limit), on a Y4_STACK_SIZE-entry stack: refuse a tree
+	// they could overflow instead of corrupting memory
+	ctx->bvh_levels = levels;
 	if(levels > Y4_STACK_SIZE - 8)
 	{
 		ctx->err = "BVH8 is deeper than the traversal stack (degenerate input: very many coincident triangles)";
@@ -502,7 +504,7 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 	float ms = 0.f;
 	cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
 	ctx->stats.build_ms = ms;
-	ctx->stats.n_tris = n; ctx->stats.n_nodes = ctx->n_nodes;
+	ctx->stats.n_tris = n; ctx->stats.n_nodes = ctx->n_nodes; ctx->stats.bvh_levels = (uint64_t) levels;
 	ctx->stats.node_bytes = ctx->n_nodes * Y4_NODE_WORDS * sizeof(Y4U4);
 	ctx->stats.tri_bytes = (uint64_t) n * sizeof(Y4Tri);
 	ctx->stats.kernel_launches += 1;

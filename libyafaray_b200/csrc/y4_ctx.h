@@ -27,6 +27,7 @@ struct y4gpu_ctx
 	Y4U4 *d_nodes = nullptr;
 	Y4Tri *d_tris = nullptr;
 	uint64_t n_nodes = 0;
+	int bvh_levels = 0;                 // levels of the BVH8 (collapse rounds of the last build)
 	bool built = false;
 	float raw_bound[6] = {0, 0, 0, 0, 0, 0};
 	float bound[6] = {0, 0, 0, 0, 0, 0};
@@ -51,7 +52,7 @@ struct y4gpu_ctx
 	y4gpu_stats stats = {};
 	Y4Pt *pt = nullptr;
 
-	Y4Bvh8 view() const { Y4Bvh8 v; v.nodes = d_nodes; v.tris = d_tris; v.n_tris = (uint32_t) n_tri; v.consts = d_consts; return v; }
+	Y4Bvh8 view() const { Y4Bvh8 v; v.nodes = d_nodes; v.tris = d_tris; v.n_tris = (uint32_t) n_tri; v.consts = d_consts; v.postpone_sp_limit = Y4_STACK_SIZE - bvh_levels; return v; }
 };
 
 #define Y4_CUDA(ctx, call)                                                                       \

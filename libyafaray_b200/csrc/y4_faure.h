@@ -4,7 +4,7 @@
 //   b even: sigma_b = (2*sigma_{b/2}, 2*sigma_{b/2} + 1)
 //   b odd : sigma_b = sigma_{b-1} with values >= c=(b-1)/2 incremented and c inserted in the middle
 // and the reciprocals as 1/p rounded to 9 decimals (the reference's `inv_prims` literals).
-// tests/test_pt_kat.py checks the generated tables against reference output for all 49 dims.
+// tests/test_pt_cpu.py checks the generated tables against reference output for all 49 dims.
 #pragma once
 #include <cstdint>
 #include <cstdio>

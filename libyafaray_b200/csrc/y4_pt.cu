@@ -252,6 +252,9 @@ static bool pt_is_device_ptr(const void *p)
 	return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
+// geometry or BVH changed: the per-triangle shading arrays and the scene description are stale until the next y4gpu_pt_set_scene
+void y4_pt_invalidate(y4gpu_ctx *ctx) { if(ctx->pt) ctx->pt->scene_set = false; }
+
 extern "C" {
 
 void y4gpu_pt_release(y4gpu_ctx *ctx)
@@ -354,6 +357,9 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	// ---- the supported set; everything else is rejected, never approximated ----
 	if(n_mat == 0) { ctx->err = "no materials"; return Y4GPU_ERR_ARG; }
 	if(n_light > Y4_PT_MAX_LIGHTS) { ctx->err = "more than 64 lights"; return Y4GPU_ERR_UNSUPPORTED; }
+	if(ctx->pt) ctx->pt->scene_set = false;             // a failed call must not leave the previous scene usable with half-updated state
+	if(params->raydepth > 19) { ctx->err = "raydepth > 19 is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
+	if(params->transp_shadows && params->shadow_depth > 16) { ctx->err = "shadowDepth > 16 is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(params->bounces < 1 || params->bounces > 11) { ctx->err = "bounces must be 1..11 (sample dimensions 4*depth+4 < 50)"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(params->path_samples < 0 || params->width < 1 || params->height < 1) { ctx->err = "bad path_samples / film size"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_mat; ++i)
@@ -661,6 +667,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	std::lock_guard<std::mutex> lock(ctx->mtx);
 	Y4Pt *pt = ctx->pt;
 	if(!pt || !pt->scene_set) { ctx->err = "y4gpu_pt_render_pass before y4gpu_pt_set_scene"; return Y4GPU_ERR_ARG; }
+	if(!ctx->built) { ctx->err = "y4gpu_pt_render_pass before y4gpu_build"; return Y4GPU_ERR_ARG; }
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	cudaStream_t st = ctx->stream;
 	Y4PtScene &sc = pt->h_scene;
@@ -735,7 +742,8 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	Y4_CUDA(ctx, cudaMemsetAsync(pt->d_counters, 0, need * sizeof(unsigned long long), st));
 	pt->counter_kinds.clear(); pt->dense_closest = 0;
 	size_t next_slot = 8;
-	auto new_slot = [&]() -> unsigned long long * { return pt->d_counters + (next_slot < need ? next_slot++ : need - 1); };
+	bool slot_overflow = false;       // the estimate `need` was too small: a launch would share a counter -> the pass fails instead
+	auto new_slot = [&]() -> unsigned long long * { if(next_slot >= need) { slot_overflow = true; return pt->d_counters + need - 1; } return pt->d_counters + next_slot++; };
 	// a path queue and a shadow queue filled by the same stage: adjacent halves of one 64-bit slot
 	auto new_queue_pair = [&](int kind_path, int kind_shadow, uint32_t *&path_count, uint32_t *&shadow_count)
 	{
@@ -884,6 +892,12 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 #undef Y4_PT_LAUNCH
 #undef Y4_PT_TRACE
 	st = ctx->stream;
+	if(slot_overflow)
+	{
+		for(int l = 0; l < n_lanes; ++l) cudaStreamSynchronize(pt->lanes[l].stream);
+		ctx->err = "internal: per-pass counter slots exhausted (launch sequence longer than estimated)";
+		return Y4GPU_ERR_CUDA;
+	}
 	if(n_lanes > 1)
 	{
 		// join: the context's stream continues after the other lanes

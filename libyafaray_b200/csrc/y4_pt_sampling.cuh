@@ -15,7 +15,7 @@
 // intermediates).  The device has no 80-bit type; those intermediates are evaluated in
 // fp64 (Y4_WIDE).  The only observable difference is a last-bit change of the float result
 // when the exact product lies within ~2^-53 of a rounding boundary (probability ~2^-29 per
-// operation); tests/test_pt_kat.py quantifies it against KATs taken from the reference.
+// operation); tests/test_pt_cpu.py quantifies it against KATs taken from the reference.
 #pragma once
 #include "y4_common.cuh"
 

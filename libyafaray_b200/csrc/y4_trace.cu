@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 			bool done = false;
 			while(tgroup.y)
 			{
-				if(postpone_div > 0 && sp < Y4_STACK_SIZE - 4 && __popc(__activemask()) * postpone_div < entered)
+				if(postpone_div > 0 && sp < bvh.postpone_sp_limit && __popc(__activemask()) * postpone_div < entered)
 				{
 					stack[sp++] = tgroup;
 					break;

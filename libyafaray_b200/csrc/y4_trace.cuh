@@ -18,6 +18,10 @@ struct Y4Bvh8
 	const Y4Tri *tris;     // leaf-ordered triangle records
 	uint32_t n_tris;       // 0 => empty scene
 	const uint32_t *consts; // device: [0] = 0x4B000000 (see y4_byte_m); unused on the host
+	// Stack budget of k_trace: at most one pending sibling group per tree level sits on the stack (<= levels - 1), so
+	// postponed triangle groups may only be pushed while sp < Y4_STACK_SIZE - levels.  Then T <= Y4_STACK_SIZE - levels
+	// postponed groups + G <= levels - 1 sibling groups never exceed the array (y4_build.cu refuses levels > Y4_STACK_SIZE - 8).
+	int postpone_sp_limit;
 };
 
 struct Y4TraceStats { uint32_t nodes, tris; };

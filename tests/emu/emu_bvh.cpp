@@ -89,7 +89,7 @@ int emu_build_trace(const float *verts, const uint32_t *flags, int n, const floa
 {
 	EmuBvh b;
 	emu_build(verts, flags, n, leaf_max, b);
-	Y4Bvh8 bvh; bvh.nodes = b.nodes.data(); bvh.tris = b.tris.data(); bvh.n_tris = (uint32_t) n; bvh.consts = nullptr;
+	Y4Bvh8 bvh; bvh.nodes = b.nodes.data(); bvh.tris = b.tris.data(); bvh.n_tris = (uint32_t) n; bvh.consts = nullptr; bvh.postpone_sp_limit = 0;
 	uint64_t sn = 0, st = 0;
 	for(int i = 0; i < m; ++i)
 	{

@@ -109,7 +109,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 {
 	EmuBvh b;
 	emu_build(verts, flags, n_tri, 1, b);
-	Y4Bvh8 bvh; bvh.nodes = b.nodes.data(); bvh.tris = b.tris.data(); bvh.n_tris = (uint32_t) n_tri; bvh.consts = nullptr;
+	Y4Bvh8 bvh; bvh.nodes = b.nodes.data(); bvh.tris = b.tris.data(); bvh.n_tris = (uint32_t) n_tri; bvh.consts = nullptr; bvh.postpone_sp_limit = 0;
 	static Y4FaureHost fh = y4_faure_build();
 	Y4PtScene sc;
 	memset(&sc, 0, sizeof(sc));

@@ -177,3 +177,37 @@ def test_full_size_c3_properties_and_tree_independence(monkeypatch):
     assert np.array_equal(hd["prim"][pick], exp["prim"]) and np.array_equal(hd["t"][pick], exp["t"])
     plain.close()
     acc.close()
+
+
+def test_many_scale_chain_scene_deep_tree_stack_bound():
+    """k_trace's 64-entry stack.  A scene whose triangles shrink geometrically towards one corner gives the
+    deepest hierarchy the builder can produce in fp32 (every split peels a few octaves off); sibling groups (<= levels - 1)
+    plus postponed triangle groups (pushed only while sp < 64 - levels) must fit, and the hits must equal brute force."""
+    from libyafaray_b200.accelerator import AcceleratorB200
+    rng = np.random.default_rng(7)
+    k = np.arange(0, 240, dtype=np.float64)
+    s = (0.5 ** (k / 2.0))                                   # 120 octaves of scale
+    base = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float64)
+    tris = []
+    for rep in range(12):                                    # several triangles per scale, scattered around the diagonal
+        jitter = 1.0 + 0.3 * rng.random((len(k), 1, 3))
+        rot = rng.random((len(k), 1, 3)) * 0.2
+        tris.append(((base[None] * jitter + rot) * s[:, None, None] + s[:, None, None]).reshape(len(k), 9))
+    tris = np.concatenate(tris).astype(np.float32)
+    acc = AcceleratorB200(tris)
+    levels = acc.stats()["bvh_levels"]
+    assert 1 <= levels <= 56
+    # rays from outside towards the accumulation corner, from many directions, plus rays along the diagonal
+    n = 4096
+    o = rng.normal(size=(n, 3)); o = 3.0 * o / np.linalg.norm(o, axis=1, keepdims=True)
+    target = (rng.random((n, 1)) ** 6) * np.array([[1.2, 1.2, 0.2]]) * rng.random((n, 3))
+    d = target - o; d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, 0:3] = o; rays[:, 4:7] = d; rays[:, 3] = 0.0; rays[:, 7] = -1.0
+    got, exp = acc.intersect(rays), helpers.emu_brute(tris, rays, 0)
+    assert (exp["prim"] >= 0).sum() > n // 20
+    # triangles 2^-100 across seen from distance 3 collide in fp32 t: ties / 1-ulp near-ties are the documented class
+    r = helpers.compare_closest(got, exp)
+    assert r["bad"] == 0 and r["t_out_of_tol"] == 0 and r["near_tie"] <= 16 and r["same"] >= n - 16, r
+    assert np.array_equal(acc.isShadowed(rays)["prim"] >= 0, helpers.emu_brute(tris, rays, 1)["prim"] >= 0)
+    acc.close()
