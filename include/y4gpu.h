@@ -114,6 +114,16 @@ int y4gpu_trace_counted(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_
 /* transparent shadows: mat_transparency = n_mat * 3 floats (Material::getTransparency colour) */
 int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth,
                         const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out);
+/* Allocation-free variant of y4gpu_trace (CLOSEST / SHADOW).  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  It calls no cudaMalloc / cudaFree / allocating library routine: the traversal kernel's work
+ * counter and the staging of host-resident rays / hits live in one static __device__ array of the library (3 MiB, held by
+ * every GPU that loads the library until the process exits).  n > Y4GPU_NOALLOC_MAX_RAYS is rejected with Y4GPU_ERR_ARG
+ * (split the batch, or use y4gpu_trace).  Results are identical to y4gpu_trace's.  All calls on one device share the array:
+ * calls that overlap on the GPU (different contexts or streams without ordering) race; calls on one context with host
+ * buffers are serialised by the library.  rays / out: host or device memory, like y4gpu_trace. */
+#define Y4GPU_NOALLOC_MAX_RAYS 65536
+int y4gpu_trace_noalloc(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out);
 int y4gpu_get_stats(const y4gpu_ctx *ctx, y4gpu_stats *out);
 int y4gpu_synchronize(y4gpu_ctx *ctx);
 

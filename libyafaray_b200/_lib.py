@@ -116,6 +116,9 @@ BLEND_MODES = {"mix": 0, "add": 1, "multiply": 2, "subtract": 3, "screen": 4, "d
 LAYER_RGB_TO_INT, LAYER_STENCIL, LAYER_NEGATIVE = 1, 2, 4
 
 
+NOALLOC_MAX_RAYS = 65536  # Y4GPU_NOALLOC_MAX_RAYS
+
+
 class Y4Error(RuntimeError):
     pass
 
@@ -127,7 +130,7 @@ EXPORTED = [
     "y4gpu_create", "y4gpu_destroy", "y4gpu_last_error", "y4gpu_device_count",
     "y4gpu_set_stream", "y4gpu_host_alloc", "y4gpu_host_free",
     "y4gpu_upload_triangles", "y4gpu_build", "y4gpu_get_bound",
-    "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow",
+    "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow", "y4gpu_trace_noalloc",
     "y4gpu_get_stats", "y4gpu_synchronize",
     "y4gpu_pt_set_textures", "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
     "y4gpu_pt_read_film", "y4gpu_pt_write_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass",
@@ -163,7 +166,7 @@ def lib() -> C.CDLL:
     L.y4gpu_build.restype = i32
     L.y4gpu_get_bound.argtypes = [vp, C.POINTER(C.c_float * 6)]
     L.y4gpu_get_bound.restype = i32
-    for name in ("y4gpu_trace", "y4gpu_trace_counted"):
+    for name in ("y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_noalloc"):
         f = getattr(L, name)
         f.argtypes = [vp, i32, vp, u64, vp]
         f.restype = i32

@@ -327,3 +327,93 @@ int y4_launch_tshadow(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_d
 	ctx->stats.last_trace_rays = n;
 	return Y4GPU_OK;
 }
+
+// ---- allocation-free ray batches (y4gpu_trace_noalloc) ------------------------------------------------
+// For callers that may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the scratch
+// k_trace needs -- its persistent-thread work counter, and the ray / hit staging used when the caller's buffers live in host
+// memory -- sits in ONE file-scope device array of fixed size instead of the context's cudaMalloc'ed buffers.  Every GPU that
+// loads this library holds the array (256 B + 48 B x Y4GPU_NOALLOC_MAX_RAYS = 3 MiB) until the process exits.  All calls on a
+// device share it and it keeps the last call's contents: the counter is cleared by every call (the staging areas are fully
+// overwritten before they are read), and calls that overlap ON THE GPU race.
+namespace {
+
+constexpr size_t kNoAllocHeader = 256;      // [0, 8): work counter of k_trace; the rest pads the ray area to 256 B
+constexpr size_t kNoAllocRays = kNoAllocHeader;
+constexpr size_t kNoAllocHits = kNoAllocRays + (size_t) Y4GPU_NOALLOC_MAX_RAYS * sizeof(Y4Ray);
+constexpr size_t kNoAllocBytes = kNoAllocHits + (size_t) Y4GPU_NOALLOC_MAX_RAYS * sizeof(Y4Hit);
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device (with that device current) and cached.
+std::mutex g_noalloc_mtx;
+unsigned char *g_noalloc_dev[64] = {nullptr};
+
+int noalloc_scratch(y4gpu_ctx *ctx, unsigned char **out)
+{
+	if(ctx->device < 0 || ctx->device >= 64) { ctx->err = "y4gpu_trace_noalloc: device index out of range"; return Y4GPU_ERR_ARG; }
+	std::lock_guard<std::mutex> lock(g_noalloc_mtx);
+	if(!g_noalloc_dev[ctx->device])
+	{
+		void *p = nullptr;
+		const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);      // the current device is ctx->device (set by the caller)
+		if(e != cudaSuccess || !p)
+		{
+			ctx->err = std::string("y4gpu_trace_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e);
+			cudaGetLastError();
+			return Y4GPU_ERR_CUDA;
+		}
+		g_noalloc_dev[ctx->device] = static_cast<unsigned char *>(p);
+	}
+	*out = g_noalloc_dev[ctx->device];
+	return Y4GPU_OK;
+}
+
+bool noalloc_is_device_ptr(const void *p)
+{
+	cudaPointerAttributes a;
+	if(cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+	return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+} // namespace
+
+extern "C" int y4gpu_trace_noalloc(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out)
+{
+	if(!ctx || (n && (!rays || !out))) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	if(kind != Y4_TRACE_CLOSEST && kind != Y4_TRACE_SHADOW) { ctx->err = "y4gpu_trace_noalloc: kind must be Y4GPU_TRACE_CLOSEST or Y4GPU_TRACE_SHADOW"; return Y4GPU_ERR_ARG; }
+	if(!ctx->built) { ctx->err = "y4gpu_trace_noalloc before y4gpu_build"; return Y4GPU_ERR_ARG; }
+	if(n > (uint64_t) Y4GPU_NOALLOC_MAX_RAYS)
+	{
+		ctx->err = "y4gpu_trace_noalloc: " + std::to_string(n) + " rays exceed the static scratch (Y4GPU_NOALLOC_MAX_RAYS = " + std::to_string(Y4GPU_NOALLOC_MAX_RAYS)
+			+ "); split the batch or use y4gpu_trace";
+		return Y4GPU_ERR_ARG;
+	}
+	if(n == 0) return Y4GPU_OK;
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	unsigned char *scratch = nullptr;
+	{ const int rc = noalloc_scratch(ctx, &scratch); if(rc) return rc; }
+	cudaStream_t st = ctx->stream;
+	const bool rays_dev = noalloc_is_device_ptr(rays), out_dev = noalloc_is_device_ptr(out);
+	const Y4Ray *d_rays = reinterpret_cast<const Y4Ray *>(rays);
+	Y4Hit *d_out = reinterpret_cast<Y4Hit *>(out);
+	if(!rays_dev)
+	{
+		Y4_CUDA(ctx, cudaMemcpyAsync(scratch + kNoAllocRays, rays, n * sizeof(Y4Ray), cudaMemcpyHostToDevice, st));
+		d_rays = reinterpret_cast<const Y4Ray *>(scratch + kNoAllocRays);
+	}
+	if(!out_dev) d_out = reinterpret_cast<Y4Hit *>(scratch + kNoAllocHits);
+	// the counter must start at zero; it still holds the previous call's final value
+	Y4_CUDA(ctx, cudaMemsetAsync(scratch, 0, sizeof(unsigned long long), st));
+	TraceArgs a; a.rays = d_rays; a.n = n; a.out = d_out; a.work_counter = reinterpret_cast<unsigned long long *>(scratch);
+	a.visit = nullptr; a.queue = nullptr; a.queue_count = nullptr; a.stream = st; a.max_blocks_per_sm = 0;
+	const int rc = kind == Y4_TRACE_CLOSEST ? launch<Y4_TRACE_CLOSEST, false>(ctx, false, a) : launch<Y4_TRACE_SHADOW, false>(ctx, false, a);
+	if(rc) return rc;
+	Y4_CUDA(ctx, cudaGetLastError());
+	ctx->stats.kernel_launches++;
+	if(!out_dev) Y4_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * sizeof(Y4Hit), cudaMemcpyDeviceToHost, st));
+	// host buffers: the call is synchronous like y4gpu_trace; device buffers: queued on the context's stream, not waited for
+	if(!out_dev || !rays_dev) Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	return Y4GPU_OK;
+}
