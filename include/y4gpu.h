@@ -107,13 +107,24 @@ int y4gpu_build(y4gpu_ctx *ctx, const y4gpu_build_params *params /* nullable */)
 int y4gpu_get_bound(const y4gpu_ctx *ctx, float out_bound[6]);
 
 /* ray batches ---------------------------------------------------------------------------- */
-/* rays/out may each be host or device memory (detected); out has n records. */
+/* rays/out may each be host or device memory (detected); out has n records.
+ * Host rays AND host hits: the call is synchronous and RE-ENTRANT -- any number of host threads may call it on one context
+ * concurrently (the Accelerator virtuals are called from every render thread, integrator_tiled.cc:248-251); each call runs on
+ * a private slot of the context (own streams, staging, work counters).  Batches of >= 2^19 rays are cut into chunks whose
+ * H2D copy, traversal and D2H copy overlap on several streams (pass page-locked buffers, y4gpu_host_alloc, for that).
+ * Device buffers: queued on the context's stream, not waited for; such calls are serialised by the context's mutex. */
 int y4gpu_trace(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out);
 /* same, plus per-batch node/triangle visit counters in y4gpu_stats (slower; for the roofline) */
 int y4gpu_trace_counted(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out);
 /* transparent shadows: mat_transparency = n_mat * 3 floats (Material::getTransparency colour) */
 int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth,
                         const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out);
+/* The same query with the arguments of the INNER virtual Accelerator::intersectTs(sray, max_depth, dist, ...)
+ * (accelerator_kdtree.cc:911-1061), which receives the ray after the wrapper advanced its origin: no origin shift here,
+ * accept ray.tmin <= t < ray.tmax (tmax = dist).  For the inner closest / shadow virtuals y4gpu_trace already fits:
+ * intersect(ray, t_max) = CLOSEST with tmax = t_max, intersectS(sray, t_max, bias) = SHADOW with tmin = 0, tmax = t_max. */
+int y4gpu_trace_tshadow_inner(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth,
+                              const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out);
 /* Allocation-free variant of y4gpu_trace (CLOSEST / SHADOW).  It has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  It calls no cudaMalloc / cudaFree / allocating library routine: the traversal kernel's work

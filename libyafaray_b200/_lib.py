@@ -130,7 +130,7 @@ EXPORTED = [
     "y4gpu_create", "y4gpu_destroy", "y4gpu_last_error", "y4gpu_device_count",
     "y4gpu_set_stream", "y4gpu_host_alloc", "y4gpu_host_free",
     "y4gpu_upload_triangles", "y4gpu_build", "y4gpu_get_bound",
-    "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow", "y4gpu_trace_noalloc",
+    "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow", "y4gpu_trace_tshadow_inner", "y4gpu_trace_noalloc",
     "y4gpu_get_stats", "y4gpu_synchronize",
     "y4gpu_pt_set_textures", "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
     "y4gpu_pt_read_film", "y4gpu_pt_write_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass",
@@ -172,6 +172,8 @@ def lib() -> C.CDLL:
         f.restype = i32
     L.y4gpu_trace_tshadow.argtypes = [vp, vp, u64, i32, vp, u32, vp]
     L.y4gpu_trace_tshadow.restype = i32
+    L.y4gpu_trace_tshadow_inner.argtypes = [vp, vp, u64, i32, vp, u32, vp]
+    L.y4gpu_trace_tshadow_inner.restype = i32
     L.y4gpu_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.y4gpu_get_stats.restype = i32
     L.y4gpu_synchronize.argtypes = [vp]

@@ -5,6 +5,7 @@
 #include <cstdlib>
 
 static std::string g_create_err;
+extern "C" { static void slot_free_all(y4gpu_ctx *ctx); }
 
 static bool is_device_ptr(const void *p)
 {
@@ -73,6 +74,7 @@ void y4gpu_destroy(y4gpu_ctx *ctx)
 	cudaSetDevice(ctx->device);
 	if(ctx->stream) cudaStreamSynchronize(ctx->stream);
 	y4gpu_pt_release(ctx);
+	slot_free_all(ctx);
 	cudaFree(ctx->d_verts); cudaFree(ctx->d_flags); cudaFree(ctx->d_nodes); cudaFree(ctx->d_tris);
 	cudaFree(ctx->d_rays); cudaFree(ctx->d_hits); cudaFree(ctx->d_work_counter); cudaFree(ctx->d_visit_counters); cudaFree(ctx->d_consts);
 	cudaFree(ctx->d_mat_transp);
@@ -154,14 +156,178 @@ static int ensure_stage(y4gpu_ctx *ctx, uint64_t n, uint64_t hit_bytes)
 	return Y4GPU_OK;
 }
 
+// ---- slot pool: the re-entrant host-buffer path ---------------------------------------------------------
+// The Accelerator virtuals are called concurrently by every render thread (integrator_tiled.cc:248-251).  A call with host
+// buffers takes a private slot (streams, device staging, work counters, pinned staging), so concurrent calls share nothing
+// but the read-only BVH; the context mutex is not held while the GPU works.  Errors are reported per call through the
+// return code; the message goes to ctx->err under the statistics lock (last writer wins).
+static void slot_error(y4gpu_ctx *ctx, const std::string &msg) { std::lock_guard<std::mutex> lk(ctx->stat_mtx); ctx->err = msg; }
+#define Y4_SLOT_CUDA(ctx, call)                                                                  \
+	do {                                                                                         \
+		const cudaError_t e_ = (call);                                                           \
+		if(e_ != cudaSuccess) { slot_error(ctx, std::string(#call) + ": " + cudaGetErrorString(e_)); return Y4GPU_ERR_CUDA; } \
+	} while(0)
+
+static int slot_acquire(y4gpu_ctx *ctx, Y4TraceSlot **out)
+{
+	{
+		std::lock_guard<std::mutex> lk(ctx->slot_mtx);
+		if(!ctx->free_slots.empty()) { *out = ctx->free_slots.back(); ctx->free_slots.pop_back(); return Y4GPU_OK; }
+	}
+	Y4TraceSlot *s = new Y4TraceSlot;
+	bool ok = cudaEventCreate(&s->ev0) == cudaSuccess && cudaEventCreate(&s->ev1) == cudaSuccess
+		&& cudaMalloc(&s->d_counters, Y4TraceSlot::kMaxChunks * sizeof(unsigned long long)) == cudaSuccess;
+	for(int i = 0; ok && i < Y4TraceSlot::kStreams; ++i)
+		ok = cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking) == cudaSuccess && cudaEventCreateWithFlags(&s->ev_join[i], cudaEventDisableTiming) == cudaSuccess;
+	{
+		std::lock_guard<std::mutex> lk(ctx->slot_mtx);
+		ctx->all_slots.push_back(s);              // owned by the context from here on (freed in y4gpu_destroy)
+	}
+	if(!ok) { slot_error(ctx, std::string("trace slot setup failed: ") + cudaGetErrorString(cudaGetLastError())); return Y4GPU_ERR_CUDA; }
+	*out = s;
+	return Y4GPU_OK;
+}
+static void slot_release(y4gpu_ctx *ctx, Y4TraceSlot *s)
+{
+	std::lock_guard<std::mutex> lk(ctx->slot_mtx);
+	ctx->free_slots.push_back(s);
+}
+static void slot_free_all(y4gpu_ctx *ctx)
+{
+	for(Y4TraceSlot *s : ctx->all_slots)
+	{
+		for(int i = 0; i < Y4TraceSlot::kStreams; ++i)
+		{
+			if(s->streams[i]) { cudaStreamSynchronize(s->streams[i]); cudaStreamDestroy(s->streams[i]); }
+			if(s->ev_join[i]) cudaEventDestroy(s->ev_join[i]);
+		}
+		if(s->ev0) cudaEventDestroy(s->ev0);
+		if(s->ev1) cudaEventDestroy(s->ev1);
+		cudaFree(s->d_rays); cudaFree(s->d_hits); cudaFree(s->d_counters); cudaFree(s->d_mat_transp);
+		if(s->h_pinned) cudaFreeHost(s->h_pinned);
+		delete s;
+	}
+	ctx->all_slots.clear(); ctx->free_slots.clear();
+}
+static int slot_ensure(y4gpu_ctx *ctx, Y4TraceSlot *s, uint64_t n, uint64_t hit_bytes)
+{
+	if(n > s->cap_rays)
+	{
+		cudaFree(s->d_rays); s->d_rays = nullptr; s->cap_rays = 0;
+		const uint64_t cap = n < 4096 ? 4096 : n;
+		Y4_SLOT_CUDA(ctx, cudaMalloc(&s->d_rays, cap * sizeof(Y4Ray)));
+		s->cap_rays = cap;
+	}
+	if(n * hit_bytes > s->cap_hit_bytes)
+	{
+		cudaFree(s->d_hits); s->d_hits = nullptr; s->cap_hit_bytes = 0;
+		const uint64_t cap = n * hit_bytes < 4096 * 32 ? 4096 * 32 : n * hit_bytes;
+		Y4_SLOT_CUDA(ctx, cudaMalloc(&s->d_hits, cap));
+		s->cap_hit_bytes = cap;
+	}
+	return Y4GPU_OK;
+}
+
+constexpr uint64_t kSmallBatch = 2048;          // up to here rays / hits are staged through the slot's pinned buffer
+constexpr uint64_t kMinChunk = 1ull << 18;      // rays per pipelined chunk, at least
+
+// Host rays in, host hits out.  Small batches: one stream, pinned staging.  Large batches: the batch is cut into chunks that
+// go round-robin over the slot's streams (H2D copy -> kernel -> D2H copy per chunk), so the copies of one chunk overlap the
+// traversal of another and both copy engines stay busy; the caller's buffers should be page-locked (y4gpu_host_alloc) for the
+// copies to be asynchronous.  tshadow: mat != null.
+static int trace_host(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, void *out, uint64_t hit_bytes,
+                      int max_depth, const float *mat_transparency, uint32_t n_mat, bool inner)
+{
+	Y4TraceSlot *s = nullptr;
+	{ const int rc = slot_acquire(ctx, &s); if(rc) return rc; }
+	struct Release { y4gpu_ctx *c; Y4TraceSlot *s; ~Release() { for(int i = 0; i < Y4TraceSlot::kStreams; ++i) cudaStreamSynchronize(s->streams[i]); slot_release(c, s); } } release{ctx, s};
+	{ const int rc = slot_ensure(ctx, s, n, hit_bytes); if(rc) return rc; }
+	const bool tshadow = kind == Y4_TRACE_TSHADOW;
+	if(tshadow && n_mat)
+	{
+		if(n_mat > s->mat_transp_cap)
+		{
+			cudaFree(s->d_mat_transp); s->d_mat_transp = nullptr; s->mat_transp_cap = 0;
+			Y4_SLOT_CUDA(ctx, cudaMalloc(&s->d_mat_transp, (size_t) n_mat * 3 * sizeof(float)));
+			s->mat_transp_cap = n_mat;
+		}
+		Y4_SLOT_CUDA(ctx, cudaMemcpyAsync(s->d_mat_transp, mat_transparency, (size_t) n_mat * 3 * sizeof(float), cudaMemcpyDefault, s->streams[0]));
+	}
+	uint64_t n_chunks = 1, chunk = n;
+	if(n >= 2 * kMinChunk)
+	{
+		n_chunks = n / kMinChunk;
+		if(n_chunks > 16) n_chunks = 16;
+		chunk = ((n + n_chunks - 1) / n_chunks + 31) & ~31ull;
+		n_chunks = (n + chunk - 1) / chunk;
+	}
+	cudaStream_t s0 = s->streams[0];
+	Y4_SLOT_CUDA(ctx, cudaMemsetAsync(s->d_counters, 0, n_chunks * sizeof(unsigned long long), s0));
+	Y4_SLOT_CUDA(ctx, cudaEventRecord(s->ev0, s0));
+	const int n_streams = n_chunks > 1 ? Y4TraceSlot::kStreams : 1;
+	for(int i = 1; i < n_streams; ++i) Y4_SLOT_CUDA(ctx, cudaStreamWaitEvent(s->streams[i], s->ev0, 0));
+	const bool small = n <= kSmallBatch;
+	char *h_stage = nullptr;
+	if(small)
+	{
+		const size_t need = n * (sizeof(Y4Ray) + hit_bytes);
+		if(need > s->pinned_bytes)
+		{
+			if(s->h_pinned) cudaFreeHost(s->h_pinned);
+			s->h_pinned = nullptr; s->pinned_bytes = 0;
+			const size_t cap = kSmallBatch * (sizeof(Y4Ray) + 32);
+			Y4_SLOT_CUDA(ctx, cudaMallocHost(&s->h_pinned, cap));
+			s->pinned_bytes = cap;
+		}
+		h_stage = static_cast<char *>(s->h_pinned);
+		memcpy(h_stage, rays, n * sizeof(Y4Ray));
+	}
+	for(uint64_t c = 0; c < n_chunks; ++c)
+	{
+		cudaStream_t st = s->streams[c % (uint64_t) n_streams];
+		const uint64_t first = c * chunk, cnt = (n - first) < chunk ? (n - first) : chunk;
+		Y4_SLOT_CUDA(ctx, cudaMemcpyAsync(s->d_rays + first, small ? (const void *) h_stage : (const void *) (rays + first), cnt * sizeof(Y4Ray), cudaMemcpyHostToDevice, st));
+		char *d_hits = static_cast<char *>(s->d_hits) + first * hit_bytes;
+		int rc;
+		if(tshadow) rc = y4_launch_tshadow_on(ctx, s->d_rays + first, cnt, max_depth, s->d_mat_transp, n_mat, reinterpret_cast<y4gpu_tshit *>(d_hits), inner, s->d_counters + c, st);
+		else rc = y4_launch_trace_on(ctx, kind, s->d_rays + first, cnt, reinterpret_cast<Y4Hit *>(d_hits), s->d_counters + c, st);
+		if(rc) return rc;
+		char *h_dst = small ? h_stage + n * sizeof(Y4Ray) : static_cast<char *>(out) + first * hit_bytes;
+		Y4_SLOT_CUDA(ctx, cudaMemcpyAsync(h_dst, d_hits, cnt * hit_bytes, cudaMemcpyDeviceToHost, st));
+	}
+	for(int i = 1; i < n_streams; ++i)
+	{
+		Y4_SLOT_CUDA(ctx, cudaEventRecord(s->ev_join[i], s->streams[i]));
+		Y4_SLOT_CUDA(ctx, cudaStreamWaitEvent(s0, s->ev_join[i], 0));
+	}
+	Y4_SLOT_CUDA(ctx, cudaEventRecord(s->ev1, s0));
+	Y4_SLOT_CUDA(ctx, cudaStreamSynchronize(s0));
+	if(small) memcpy(out, h_stage + n * sizeof(Y4Ray), n * hit_bytes);
+	float ms = 0.f;
+	cudaEventElapsedTime(&ms, s->ev0, s->ev1);
+	{
+		std::lock_guard<std::mutex> lk(ctx->stat_mtx);
+		ctx->stats.kernel_launches += n_chunks;
+		ctx->stats.last_trace_rays = n;
+		ctx->stats.last_trace_ms = ms;          // copies included (the whole pipelined batch)
+		ctx->last_trace_async = false;
+	}
+	return Y4GPU_OK;
+}
+
 static int trace_impl(y4gpu_ctx *ctx, int kind, bool counted, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out)
 {
 	if(!ctx || (n && (!rays || !out))) return Y4GPU_ERR_ARG;
-	std::lock_guard<std::mutex> lock(ctx->mtx);
-	if(!ctx->built) { ctx->err = "y4gpu_trace before y4gpu_build"; return Y4GPU_ERR_ARG; }
+	if(kind != Y4_TRACE_CLOSEST && kind != Y4_TRACE_SHADOW) { slot_error(ctx, "bad trace kind"); return Y4GPU_ERR_ARG; }
+	if(!ctx->built) { slot_error(ctx, "y4gpu_trace before y4gpu_build"); return Y4GPU_ERR_ARG; }
 	if(n == 0) return Y4GPU_OK;
-	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	if(cudaSetDevice(ctx->device) != cudaSuccess) { slot_error(ctx, "cudaSetDevice failed"); return Y4GPU_ERR_CUDA; }
 	const bool rays_dev = is_device_ptr(rays), out_dev = is_device_ptr(out);
+	// host buffers on both sides, and the context runs on its own stream (a caller-installed stream orders the work against
+	// the caller's: keep it on that stream): the re-entrant path
+	if(!rays_dev && !out_dev && !counted && ctx->stream == ctx->own_stream)
+		return trace_host(ctx, kind, rays, n, out, sizeof(Y4Hit), 0, nullptr, 0, false);
+	std::lock_guard<std::mutex> lock(ctx->mtx);
 	if(!rays_dev || !out_dev) { const int rc = ensure_stage(ctx, n, sizeof(Y4Hit)); if(rc) return rc; }
 	const Y4Ray *d_rays = reinterpret_cast<const Y4Ray *>(rays);
 	Y4Hit *d_out = reinterpret_cast<Y4Hit *>(out);
@@ -173,6 +339,7 @@ static int trace_impl(y4gpu_ctx *ctx, int kind, bool counted, const y4gpu_ray *r
 	if(!out_dev) d_out = reinterpret_cast<Y4Hit *>(ctx->d_hits);
 	const int rc = y4_launch_trace(ctx, kind, counted, d_rays, n, d_out);
 	if(rc) return rc;
+	ctx->last_trace_async = true;
 	if(!out_dev) Y4_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * sizeof(Y4Hit), cudaMemcpyDeviceToHost, ctx->stream));
 	if(!out_dev || !rays_dev || counted) Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	if(counted)
@@ -187,15 +354,17 @@ static int trace_impl(y4gpu_ctx *ctx, int kind, bool counted, const y4gpu_ray *r
 int y4gpu_trace(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out) { return trace_impl(ctx, kind, false, rays, n, out); }
 int y4gpu_trace_counted(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out) { return trace_impl(ctx, kind, true, rays, n, out); }
 
-int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth, const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out)
+static int tshadow_impl(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth, const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out, bool inner)
 {
 	if(!ctx || (n && (!rays || !out)) || (n_mat && !mat_transparency) || max_depth < 0) return Y4GPU_ERR_ARG;
-	std::lock_guard<std::mutex> lock(ctx->mtx);
-	if(max_depth > 16) { ctx->err = "y4gpu_trace_tshadow: max_depth > 16 is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
-	if(!ctx->built) { ctx->err = "y4gpu_trace_tshadow before y4gpu_build"; return Y4GPU_ERR_ARG; }
+	if(max_depth > 16) { slot_error(ctx, "y4gpu_trace_tshadow: max_depth > 16 is not supported"); return Y4GPU_ERR_UNSUPPORTED; }
+	if(!ctx->built) { slot_error(ctx, "y4gpu_trace_tshadow before y4gpu_build"); return Y4GPU_ERR_ARG; }
 	if(n == 0) return Y4GPU_OK;
-	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	if(cudaSetDevice(ctx->device) != cudaSuccess) { slot_error(ctx, "cudaSetDevice failed"); return Y4GPU_ERR_CUDA; }
 	const bool rays_dev = is_device_ptr(rays), out_dev = is_device_ptr(out);
+	if(!rays_dev && !out_dev && ctx->stream == ctx->own_stream)
+		return trace_host(ctx, Y4_TRACE_TSHADOW, rays, n, out, sizeof(y4gpu_tshit), max_depth, mat_transparency, n_mat, inner);
+	std::lock_guard<std::mutex> lock(ctx->mtx);
 	if(!rays_dev || !out_dev) { const int rc = ensure_stage(ctx, n, sizeof(y4gpu_tshit)); if(rc) return rc; }
 	if(n_mat > ctx->mat_transp_cap)
 	{
@@ -212,11 +381,24 @@ int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int m
 		d_rays = ctx->d_rays;
 	}
 	if(!out_dev) d_out = reinterpret_cast<y4gpu_tshit *>(ctx->d_hits);
-	const int rc = y4_launch_tshadow(ctx, d_rays, n, max_depth, ctx->d_mat_transp, n_mat, d_out);
+	Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_work_counter, 0, sizeof(unsigned long long), ctx->stream));
+	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+	const int rc = y4_launch_tshadow_on(ctx, d_rays, n, max_depth, ctx->d_mat_transp, n_mat, d_out, inner, reinterpret_cast<unsigned long long *>(ctx->d_work_counter), ctx->stream);
 	if(rc) return rc;
+	Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+	ctx->stats.kernel_launches++; ctx->stats.last_trace_rays = n; ctx->last_trace_async = true;
 	if(!out_dev) Y4_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * sizeof(y4gpu_tshit), cudaMemcpyDeviceToHost, ctx->stream));
 	Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	return Y4GPU_OK;
+}
+
+int y4gpu_trace_tshadow(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth, const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out)
+{
+	return tshadow_impl(ctx, rays, n, max_depth, mat_transparency, n_mat, out, false);
+}
+int y4gpu_trace_tshadow_inner(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth, const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out)
+{
+	return tshadow_impl(ctx, rays, n, max_depth, mat_transparency, n_mat, out, true);
 }
 
 int y4gpu_set_stream(y4gpu_ctx *ctx, void *cuda_stream)
@@ -242,8 +424,12 @@ int y4gpu_get_stats(const y4gpu_ctx *ctx, y4gpu_stats *out)
 	if(!ctx || !out) return Y4GPU_ERR_ARG;
 	*out = ctx->stats;
 	float ms = 0.f;
-	if(ctx->stats.last_trace_rays && cudaEventQuery(ctx->ev1) == cudaSuccess && cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess) out->last_trace_ms = ms;
-	else cudaGetLastError();
+	// a batch queued on the context's stream is timed by its events once they have completed; the slot path stores its time directly
+	if(ctx->last_trace_async)
+	{
+		if(ctx->stats.last_trace_rays && cudaEventQuery(ctx->ev1) == cudaSuccess && cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess) out->last_trace_ms = ms;
+		else cudaGetLastError();
+	}
 	return Y4GPU_OK;
 }
 

@@ -3,10 +3,26 @@
 #include <cuda_runtime.h>
 #include <mutex>
 #include <string>
+#include <vector>
 #include "y4_trace.cuh"
 #include "../../include/y4gpu.h"
 
 struct Y4Pt;   // wavefront path tracer state (y4_pt.cu)
+
+// Everything one host-buffer ray batch needs, so that concurrent callers (the Accelerator virtuals are called from every
+// render thread, integrator_tiled.cc:248-251) never share a stream, a staging buffer or a work counter.  Slots are pooled
+// per context; a call takes one off the free list (or creates it) and puts it back when its streams have drained.
+struct Y4TraceSlot
+{
+	static constexpr int kStreams = 4, kMaxChunks = 64;
+	cudaStream_t streams[kStreams] = {nullptr, nullptr, nullptr, nullptr};
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_join[kStreams] = {nullptr, nullptr, nullptr, nullptr};
+	Y4Ray *d_rays = nullptr; void *d_hits = nullptr;
+	uint64_t cap_rays = 0, cap_hit_bytes = 0;
+	unsigned long long *d_counters = nullptr;        // kMaxChunks work counters
+	float *d_mat_transp = nullptr; uint32_t mat_transp_cap = 0;
+	void *h_pinned = nullptr; size_t pinned_bytes = 0;   // staging of small batches (1-ray calls): truly asynchronous copies
+};
 
 struct y4gpu_ctx
 {
@@ -50,6 +66,10 @@ struct y4gpu_ctx
 	int treelet_leaves = 2048;  // SAH rebuild of the binary subtrees with at most this many leaves (0 = plain LBVH; env Y4GPU_TREELET, <= 4096)
 
 	y4gpu_stats stats = {};
+	bool last_trace_async = false;             // the last batch ran on the context's stream and is timed by ev0 / ev1
+	std::mutex stat_mtx;                       // guards `stats` updates of the slot path
+	std::mutex slot_mtx;                       // guards the slot pool
+	std::vector<Y4TraceSlot *> free_slots, all_slots;
 	Y4Pt *pt = nullptr;
 
 	Y4Bvh8 view() const { Y4Bvh8 v; v.nodes = d_nodes; v.tris = d_tris; v.n_tris = (uint32_t) n_tri; v.consts = d_consts; v.postpone_sp_limit = Y4_STACK_SIZE - bvh_levels; return v; }
@@ -75,3 +95,7 @@ int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_
 int y4_launch_tshadow_wave(y4gpu_ctx *ctx, const Y4Ray *d_rays, Y4Hit *d_out, const uint32_t *d_queue, const uint32_t *d_queue_count, int max_depth,
                            const float *d_mat_transp, uint32_t n_mat, unsigned long long *d_work_counter, cudaStream_t stream, int max_blocks_per_sm);
 int y4_launch_tshadow(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out);
+// launches on an explicit stream with an explicit (pre-zeroed) work counter: the re-entrant host-buffer path of y4_api.cu
+int y4_launch_trace_on(y4gpu_ctx *ctx, int kind, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out, unsigned long long *d_work_counter, cudaStream_t stream);
+int y4_launch_tshadow_on(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out,
+                         bool inner, unsigned long long *d_work_counter, cudaStream_t stream);

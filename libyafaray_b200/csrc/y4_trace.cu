@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 // more than max_depth transparent layers means shadowed.
 __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, const Y4Ray *__restrict__ rays, uint64_t n, int max_depth,
                                                                  const float *__restrict__ mat_transp, uint32_t n_mat, y4gpu_tshit *__restrict__ out,
-                                                                 uint32_t *__restrict__ work_counter)
+                                                                 uint32_t *__restrict__ work_counter, int inner)
 {
 	const uint32_t lane = threadIdx.x & 31u;
 	uint2 stack[Y4_STACK_SIZE];
@@ -170,7 +170,13 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, con
 		const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + i));
 		const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + i) + 1);
 		Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
-		const Y4PreparedRay pr = y4_prepare_ray(r, Y4_TRACE_TSHADOW);
+		Y4PreparedRay pr = y4_prepare_ray(r, Y4_TRACE_TSHADOW);
+		if(inner)
+		{
+			// the arguments of the inner virtual intersectTs(sray, max_depth, dist, ...) (accelerator_kdtree.cc:911-1061): the origin was
+			// advanced by the wrapper already, accept sray.tmin <= t < dist
+			pr.o = v3(r.ox, r.oy, r.oz); pr.t_lo = r.tmin; pr.t_hi = (r.tmax >= 0.f) ? r.tmax : INFINITY;
+		}
 		Y4Hit h; int n_filt = 0;
 		y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, h, stack, nullptr, filt, filt_mat, &n_filt, max_depth);
 		float fr = 1.f, fg = 1.f, fb = 1.f;
@@ -320,11 +326,38 @@ int y4_launch_tshadow(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_d
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
 	const uint64_t want = (n + kTraceThreads - 1) / kTraceThreads;
 	const uint64_t full = (uint64_t) ctx->sm_count * 4;
-	k_trace_tshadow<<<(int) (want < full ? want : full), kTraceThreads, 0, st>>>(ctx->view(), d_rays, n, max_depth, d_mat_transp, n_mat, d_out, ctx->d_work_counter);
+	k_trace_tshadow<<<(int) (want < full ? want : full), kTraceThreads, 0, st>>>(ctx->view(), d_rays, n, max_depth, d_mat_transp, n_mat, d_out, ctx->d_work_counter, 0);
 	Y4_CUDA(ctx, cudaGetLastError());
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
 	ctx->stats.kernel_launches++;
 	ctx->stats.last_trace_rays = n;
+	return Y4GPU_OK;
+}
+
+// Re-entrant launches: explicit stream and work counter (zeroed by the caller on that stream), no context state touched.
+int y4_launch_trace_on(y4gpu_ctx *ctx, int kind, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out, unsigned long long *d_work_counter, cudaStream_t stream)
+{
+	if(n == 0) return Y4GPU_OK;
+	TraceArgs a; a.rays = d_rays; a.n = n; a.out = d_out; a.work_counter = d_work_counter; a.visit = nullptr; a.queue = nullptr; a.queue_count = nullptr;
+	a.stream = stream; a.max_blocks_per_sm = 0;
+	int rc;
+	if(kind == Y4_TRACE_CLOSEST) rc = launch<Y4_TRACE_CLOSEST, false>(ctx, false, a);
+	else if(kind == Y4_TRACE_SHADOW) rc = launch<Y4_TRACE_SHADOW, false>(ctx, false, a);
+	else { ctx->err = "bad trace kind"; return Y4GPU_ERR_ARG; }
+	if(rc) return rc;
+	Y4_CUDA(ctx, cudaGetLastError());
+	return Y4GPU_OK;
+}
+
+int y4_launch_tshadow_on(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out,
+                         bool inner, unsigned long long *d_work_counter, cudaStream_t stream)
+{
+	if(n == 0) return Y4GPU_OK;
+	const uint64_t want = (n + kTraceThreads - 1) / kTraceThreads;
+	const uint64_t full = (uint64_t) ctx->sm_count * 4;
+	k_trace_tshadow<<<(int) (want < full ? want : full), kTraceThreads, 0, stream>>>(ctx->view(), d_rays, n, max_depth, d_mat_transp, n_mat, d_out,
+	                                                                                   reinterpret_cast<uint32_t *>(d_work_counter), inner ? 1 : 0);
+	Y4_CUDA(ctx, cudaGetLastError());
 	return Y4GPU_OK;
 }
 

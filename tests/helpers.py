@@ -201,3 +201,42 @@ def emu_adaptive_render(yi):
             if threshold > 0:
                 changed = True
     return interface.normalize_film(film[0], film[1]), hist
+
+
+# ---- the compiled libYafaRay plug-ins (integration/: AcceleratorB200 + PathIntegratorB200 inside a patched copy of the reference) ----
+B200_DIR = os.path.join(ROOT, "integration", "_build")
+
+
+def have_plugin(name="b200_render"):
+    return os.path.exists(os.path.join(B200_DIR, name))
+
+
+def b200_render(recorder, gpu_integrator=True, cwd=None, env=None):
+    """Replays a recorded C-API script through the REFERENCE'S OWN C API of the patched libYafaRay build.  The script must set
+    scene_accelerator = yafaray-b200-bvh8; gpu_integrator selects PathIntegratorB200 (YAFARAY_B200_BACKEND=1) instead of the
+    reference's CPU PathIntegrator over the GPU accelerator's single-ray virtuals.  -> (float32 [H, W, 4], info)."""
+    with tempfile.TemporaryDirectory() as d:
+        sp, op = os.path.join(d, "scene.script"), os.path.join(d, "out.f32")
+        with open(sp, "w") as f:
+            f.write("\n".join(recorder.lines) + f"\nrender {op}\n")
+        e = dict(os.environ)
+        e["YAFARAY_B200_BACKEND"] = "1" if gpu_integrator else "0"
+        e.update(env or {})
+        out = subprocess.run([os.path.join(B200_DIR, "b200_render"), sp], capture_output=True, text=True, env=e, cwd=cwd)
+        if out.returncode != 0:
+            raise RuntimeError(f"b200_render failed rc={out.returncode}: {out.stdout[-2000:]} {out.stderr[-2000:]}")
+        info = json.loads(out.stdout.strip().splitlines()[-1])
+        img = np.fromfile(op, np.float32).reshape(info["height"], info["width"], 4)
+        return img, info
+
+
+def b200_raybatch(tris, rays, kind, threads=8, accel="yafaray-b200-bvh8"):
+    """Accelerator::factory(type) + intersect / isShadowed called from `threads` host threads of the patched libYafaRay build."""
+    with tempfile.TemporaryDirectory() as d:
+        tp, rp, hp = (os.path.join(d, n) for n in ("t.f32", "r.f32", "h.bin"))
+        np.ascontiguousarray(tris, np.float32).tofile(tp)
+        np.ascontiguousarray(rays, np.float32).tofile(rp)
+        out = subprocess.run([os.path.join(B200_DIR, "b200_raybatch"), tp, rp, kind, hp, str(threads), accel], capture_output=True, text=True)
+        if out.returncode != 0:
+            raise RuntimeError(f"b200_raybatch failed rc={out.returncode}: {out.stdout[-2000:]} {out.stderr[-2000:]}")
+        return np.fromfile(hp, HIT_DTYPE), json.loads(out.stdout.strip().splitlines()[-1])

@@ -53,3 +53,20 @@ def test_product_does_not_import_oracle():
             else:
                 assert not re.search(r"#include[^\n]*(oracle|tests/)", src), f
                 assert "oracle/" not in src or f != "Makefile", f
+
+
+def test_plugin_build_without_a_gpu_fails_the_render_and_does_not_fall_back_to_the_kdtree():
+    """The patched libYafaRay (integration/) with scene_accelerator = yafaray-b200-bvh8 on a machine without a CUDA device:
+    Accelerator::factory must NOT build a kd-tree silently (accelerator.cc:46-51 does for unknown types); yafaray_render fails."""
+    import pytest
+    import torch
+
+    import helpers
+    from libyafaray_b200 import scenes_pt
+
+    if torch.cuda.is_available() or not helpers.have_plugin():
+        pytest.skip("needs the plug-in build and no GPU")
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, accelerator="yafaray-b200-bvh8", width=32, height=18, spp=1, bounces=4)
+    img, info = helpers.b200_render(rec, gpu_integrator=False)
+    assert info["width"] == 0 and img.size == 0
