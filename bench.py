@@ -32,6 +32,7 @@ METRIC = "path-traced Msamples/s (Cornell box 1920x1080, 8 bounces + NEE, refere
 UNIT = "Msamples/s"
 RB_METRIC = "Mrays/s (closest-hit primary + any-hit shadow + cosine-diffuse closest-hit, 1M-triangle displaced sphere)"
 RB_UNIT = "Mrays/s"
+RB_METRIC_C5 = "Mrays/s (incoherent closest-hit + any-hit segments, 50M-triangle random soup)"
 BATCHES = ("primary", "shadow", "diffuse")
 LIGHT = (2.0, 3.0, 4.0)
 SHADOW_BIAS, MIN_RAYDIST = 5.0e-4, 5.0e-5
@@ -50,38 +51,68 @@ def parse_args():
     ap.add_argument("--pt-height", type=int, default=1080)
     ap.add_argument("--pt-spp", type=int, default=16, help="samples per pixel per GPU per step (one AA pass); the config's 1024 spp = 64 such steps")
     ap.add_argument("--pt-bounces", type=int, default=8)
-    ap.add_argument("--cpu-pt-width", type=int, default=480)
-    ap.add_argument("--cpu-pt-height", type=int, default=270)
-    ap.add_argument("--cpu-pt-spp", type=int, default=4)
+    ap.add_argument("--cpu-pt-width", type=int, default=0, help="reference arm film width (0 = the GPU arm's: 1920)")
+    ap.add_argument("--cpu-pt-height", type=int, default=0)
+    ap.add_argument("--cpu-pt-spp", type=int, default=1, help="reference arm samples per pixel per step (the rate is per pixel-sample)")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c4", "c5"],
+                    help="c2 (default, the headline): Cornell path tracer + C3 ray batches; c4: 10 M-triangle instanced city at 3840x2160; "
+                         "c5: 50 M-triangle soup, incoherent closest-hit + any-hit segment batches")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: per-GPU work fixed (spp / rays per GPU); strong: the job is fixed (spp per pass / rays per batch split over the GPUs)")
+    ap.add_argument("--city-tris", type=int, default=10_000_000)
+    ap.add_argument("--soup-tris", type=int, default=50_000_000)
     ap.add_argument("--no-raybatch", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.workload == "c4" and args.pt_width == 1920 and args.pt_height == 1080:
+        args.pt_width, args.pt_height = 3840, 2160
+    if not args.cpu_pt_width:
+        args.cpu_pt_width, args.cpu_pt_height = args.pt_width, args.pt_height
+    return args
 
 
-def pt_config_dict(args):
+def pt_config_dict(args, world=1):
+    strong = args.scaling == "strong"
+    spp_gpu = args.pt_spp / world if strong else args.pt_spp
+    if args.workload == "c4":
+        what = ("C4 (BASELINE configs[3]): procedural instanced city (64 base meshes on a jittered grid through yafaray_addInstance, %d instanced "
+                "triangles + ground, flattened to world space), path tracer at %dx%d, %d bounces + NEE, one sun-like area light, gauss filter; "
+                "one step = one AA pass of %g spp per GPU" % (args.city_tris, args.pt_width, args.pt_height, args.pt_bounces, spp_gpu))
+    else:
+        what = ("C2 (BASELINE configs[1]): procedural Cornell box built through the C-API mirror, path tracer 1024 spp at "
+                "%dx%d, %d bounces, 1 area light with MIS NEE, box filter; one step = one AA pass of %g spp per GPU "
+                "(1024 spp = %d steps)" % (args.pt_width, args.pt_height, args.pt_bounces, spp_gpu, max(1, int(1024 // max(spp_gpu, 1e-9)))))
     return {
-        "workload": "C2 (BASELINE configs[1]): procedural Cornell box built through the C-API mirror, path tracer 1024 spp at "
-                    "%dx%d, %d bounces, 1 area light with MIS NEE, box filter; one step = one AA pass of %d spp per GPU "
-                    "(1024 spp = %d steps)" % (args.pt_width, args.pt_height, args.pt_bounces, args.pt_spp, max(1, 1024 // args.pt_spp)),
-        "width": args.pt_width, "height": args.pt_height, "spp_per_step_per_gpu": args.pt_spp, "bounces": args.pt_bounces,
+        "workload": what,
+        "width": args.pt_width, "height": args.pt_height, "spp_per_step_per_gpu": spp_gpu, "bounces": args.pt_bounces,
         "path_samples": 1, "russian_roulette": "off (min_bounces = bounces: the reference's deterministic mode)",
-        "samples_per_step_per_gpu": args.pt_width * args.pt_height * args.pt_spp,
+        "samples_per_step_per_gpu": args.pt_width * args.pt_height * spp_gpu,
+        "scaling": args.scaling,
         "l2": "no flush needed: the path state of the wavefronts in flight (2 x 4 Mi paths x 380 B = 3 GB) is far larger than the 126 MB L2",
         "sharding": "AA-pass samples s mod N per GPU, scene + BVH replicated, one NCCL all-reduce of the pass film (5 floats/pixel) per step",
-        "secondary": "`raybatch`: C3 (configs[2]) 1M-triangle sphere, 3 x 16 Mi ray batches per GPU per step",
+        "secondary": "`raybatch`: " + ("C5 (configs[4]) 50M-triangle soup, 2 x 16 Mi ray batches" if args.workload == "c5" else "C3 (configs[2]) 1M-triangle sphere, 3 x 16 Mi ray batches per GPU per step"),
     }
 
 
-def config_dict(args):
+def config_dict(args, world=1):
     n = args.res * args.res
+    n_gpu = n // world if args.scaling == "strong" else n
+    if args.workload == "c5":
+        return {
+            "workload": "C5 (BASELINE configs[4]): %d random triangles (centres uniform in the unit cube, edges log-uniform 1e-3..1e-2); per step 2 ray batches: "
+                        "incoherent closest-hit (uniform origins and directions) and any-hit segments between random point pairs" % args.soup_tris,
+            "n_tri": args.soup_tris, "rays_per_batch": n, "rays_per_batch_per_gpu": n_gpu, "rays_per_step_per_gpu": 2 * n_gpu, "scaling": args.scaling,
+            "l2": "no flush needed: the BVH8 (%.1f GB) and each batch (%d MiB in, %d MiB out) are far larger than the 126 MB L2" % (args.soup_tris * 72e-9, n_gpu * 32 >> 20, n_gpu * 16 >> 20),
+            "sharding": "each GPU holds the whole scene + BVH8 and traces a contiguous slice of every batch, no data-path collective",
+        }
     return {
         "workload": "C3 (BASELINE configs[2]): 1M-triangle displaced sphere; per GPU per step 3 ray batches "
                     "(coherent primary closest-hit, any-hit shadow, incoherent cosine-diffuse closest-hit)",
         "n_tri": args.nu * (args.nu // 2) * 2,
-        "rays_per_batch": n,
-        "rays_per_step_per_gpu": 3 * n,
-        "l2": "no flush needed: each batch streams %d MiB of rays in and %d MiB of hits out (> 126 MB L2)" % (n * 32 >> 20, n * 16 >> 20),
+        "rays_per_batch": n, "rays_per_batch_per_gpu": n_gpu,
+        "rays_per_step_per_gpu": 3 * n_gpu, "scaling": args.scaling,
+        "l2": "no flush needed: each batch streams %d MiB of rays in and %d MiB of hits out (> 126 MB L2)" % (n_gpu * 32 >> 20, n_gpu * 16 >> 20),
         "sharding": "independent ray batches per GPU (scene + BVH replicated), no data-path collective",
     }
 
@@ -277,28 +308,43 @@ def load_peaks():
 
 
 def raybatch_arm(args, env):
-    """C3 ray batches (device-resident + end-to-end with host buffers) -> dict on rank 0, None elsewhere."""
+    """Ray batches (device-resident + end-to-end with host buffers) -> dict on rank 0, None elsewhere.
+    workload c2 / c4: C3 (1M-triangle sphere: primary, shadow, diffuse); c5: the 50M-triangle soup (incoherent closest, any-hit segments)."""
     torch, dist = env["torch"], env["dist"]
     world, rank, local, dev, barrier, sampler = env["world"], env["rank"], env["local"], env["dev"], env["barrier"], env["sampler"]
     from libyafaray_b200 import scenes
     from libyafaray_b200.accelerator import AcceleratorB200
 
-    tris = scenes.displaced_sphere(args.nu, args.nu // 2)
+    soup = args.workload == "c5"
+    BATCHES = ("incoherent", "segment") if soup else ("primary", "shadow", "diffuse")      # noqa: N806 (shadows the module constant on purpose)
+    n_total = args.res * args.res
+    n = n_total // world if args.scaling == "strong" else n_total      # rays per batch on THIS GPU
+    first = rank * n                                                    # strong: a contiguous slice of the batch; weak: distinct rays per GPU
+    if soup:
+        tris = np.concatenate([scenes.triangle_soup(min(5_000_000, args.soup_tris - f), first=f) for f in range(0, args.soup_tris, 5_000_000)])
+    else:
+        tris = scenes.displaced_sphere(args.nu, args.nu // 2)
     acc = AcceleratorB200(tris, device=local)
     stream = torch.cuda.Stream(device=dev)
     acc.set_stream(stream.cuda_stream)
     st0 = acc.stats()
-    tris_d = torch.from_numpy(tris).to(dev)
-    n = args.res * args.res
-    kinds = {"primary": acc.intersect, "shadow": acc.isShadowed, "diffuse": acc.intersect}
-
-    # ---- set-up: batches resident in HBM ---------------------------------------------------
-    rays = {"primary": gen_primary(torch, args.res, rank, dev)}
-    hits = {b: torch.empty((n, 4), device=dev, dtype=torch.float32) for b in BATCHES}
-    torch.cuda.synchronize()
-    acc.intersect(rays["primary"], hits["primary"])
-    acc.synchronize()
-    rays["shadow"], rays["diffuse"] = gen_secondary(torch, tris_d, rays["primary"], hits["primary"], seed=0xD1F + rank)
+    tris_d = None if soup else torch.from_numpy(tris).to(dev)
+    if soup:
+        kinds = {"incoherent": acc.intersect, "segment": acc.isShadowed}
+        chunks = lambda fn: np.concatenate([fn(min(1 << 22, n - f), first=first + f) for f in range(0, n, 1 << 22)])
+        rays = {"incoherent": torch.from_numpy(chunks(scenes.incoherent_rays)).to(dev), "segment": torch.from_numpy(chunks(scenes.segment_rays)).to(dev)}
+        hits = {b: torch.empty((n, 4), device=dev, dtype=torch.float32) for b in BATCHES}
+    else:
+        kinds = {"primary": acc.intersect, "shadow": acc.isShadowed, "diffuse": acc.intersect}
+        # ---- set-up: batches resident in HBM ---------------------------------------------------
+        full = gen_primary(torch, args.res, rank if args.scaling == "weak" else 0, dev)
+        rays = {"primary": full[first:first + n].contiguous() if args.scaling == "strong" else full}
+        del full
+        hits = {b: torch.empty((n, 4), device=dev, dtype=torch.float32) for b in BATCHES}
+        torch.cuda.synchronize()
+        acc.intersect(rays["primary"], hits["primary"])
+        acc.synchronize()
+        rays["shadow"], rays["diffuse"] = gen_secondary(torch, tris_d, rays["primary"], hits["primary"], seed=0xD1F + rank)
     torch.cuda.synchronize()
 
     # visit counters (deterministic per batch) -> algorithmic bytes per ray, SURVEY.md 8(d)
@@ -332,7 +378,7 @@ def raybatch_arm(args, env):
     w1 = time.time()
     if sampler:
         sampler.mark(w0, w1)
-    total_ms = ev[0][0].elapsed_time(ev[-1][3])
+    total_ms = ev[0][0].elapsed_time(ev[-1][len(BATCHES)])
     per_ms = {b: float(np.mean([ev[k][j].elapsed_time(ev[k][j + 1]) for k in range(args.steps)])) for j, b in enumerate(BATCHES)}
     launches = acc.stats()["kernel_launches"] - launches0
     hit_frac = {b: float((hits[b][:, 3].contiguous().view(torch.int32) >= 0).float().mean()) for b in BATCHES}
@@ -363,7 +409,12 @@ def raybatch_arm(args, env):
         if sampler:
             sampler.mark(w2, w3)
         e2e_ms = e0.elapsed_time(e1)
-        same = all(bool(torch.equal(h_hits[b].view(torch.int32), hits[b].cpu().view(torch.int32))) for b in BATCHES)
+        # closest-hit batches: the host-buffer path must reproduce the resident run bit for bit; any-hit batches return whichever
+        # blocker a warp meets first (schedule-dependent by design), so they are compared by occlusion
+        same = {}
+        for b in BATCHES:
+            hh, hd = h_hits[b].view(torch.int32), hits[b].cpu().view(torch.int32)
+            same[b] = ("same occlusion: %s" % bool(torch.equal(hh[:, 3] >= 0, hd[:, 3] >= 0))) if kinds[b] == acc.isShadowed else ("bit-identical: %s" % bool(torch.equal(hh, hd)))
         e2e = {"ms": e2e_ms, "steps": e_steps, "identical_to_resident_run": same}
 
     # ---- max over ranks ------------------------------------------------------------------------
@@ -376,16 +427,16 @@ def raybatch_arm(args, env):
         peak, peak_src = load_peaks()
         dom = max(BATCHES, key=lambda b: per_ms[b])
         achieved = alg[dom]["bytes_per_ray"] * n / (per_ms[dom] * 1e-3) * 1e-9
-        value = 3.0 * n * world * args.steps / (total_ms * 1e-3) * 1e-6
+        value = float(len(BATCHES)) * n * world * args.steps / (total_ms * 1e-3) * 1e-6
         line = {
-            "metric": RB_METRIC, "value": value, "unit": RB_UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms / args.steps, "scaling": "weak", "config": config_dict(args),
+            "metric": RB_METRIC_C5 if soup else RB_METRIC, "value": value, "unit": RB_UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "scaling": args.scaling, "config": config_dict(args, world),
             "breakdown_mrays_s": {b: n / per_ms[b] * 1e-3 for b in BATCHES},
             "hit_fraction": hit_frac,
             "bvh": {k: acc.stats()[k] for k in ("n_tris", "n_nodes", "node_bytes", "tri_bytes", "build_ms")},
             "gpu_launches": int(launches),
             "roofline": {
-                "bound": "hbm", "kernel": "k_trace<%s> (%s batch)" % ("SHADOW" if dom == "shadow" else "CLOSEST", dom),
+                "bound": "hbm", "kernel": "k_trace<%s> (%s batch)" % ("SHADOW" if kinds[dom] == acc.isShadowed else "CLOSEST", dom),
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": peak_src, "launch_ms": per_ms[dom],
                 "algorithmic_bytes_per_ray": alg[dom]["bytes_per_ray"], "per_batch": alg,
@@ -394,12 +445,16 @@ def raybatch_arm(args, env):
             },
         }
         if e2e:
-            line["e2e"] = {"value": 3.0 * n * world * e2e["steps"] / (e2e_ms * 1e-3) * 1e-6, "unit": RB_UNIT,
-                           "h2d_bytes_per_step": 3 * n * 32, "d2h_bytes_per_step": 3 * n * 16, "steps": e2e["steps"],
+            line["e2e"] = {"value": float(len(BATCHES)) * n * world * e2e["steps"] / (e2e_ms * 1e-3) * 1e-6, "unit": RB_UNIT,
+                           "h2d_bytes_per_step": len(BATCHES) * n * 32, "d2h_bytes_per_step": len(BATCHES) * n * 16, "steps": e2e["steps"],
                            "identical_to_resident_run": e2e["identical_to_resident_run"],
                            "api": "AcceleratorB200.intersect/isShadowed -> y4gpu_trace with pinned host ray/hit buffers"}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and not soup:
             line.update(cpu_baseline_leg(args, torch, acc, tris, tris_d, rays, hits, kinds))
+        if soup:
+            line["cpu_baseline"] = {"value": None, "unit": RB_UNIT, "cores": 0, "kind": "reference",
+                                    "sample": "not timed in this run: yafaray-kdtree-original needs 593 s to build its tree on the 50 M triangles (tests/golden/make_golden_large.py); "
+                                              "parity at full size is pinned by tests/golden/rays_soup50m.npz"}
         acc.close()
         return line
     acc.close()
@@ -471,8 +526,15 @@ def reference_pt(args):
 def run_reference_arm(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
+    # the configuration this arm REALLY runs: the same scene, film size, bounces and light as the GPU arm, fewer samples per pixel
+    # per step (the metric is a rate per pixel-sample)
+    cfg = pt_config_dict(args)
+    cfg.update({"width": args.cpu_pt_width, "height": args.cpu_pt_height, "spp_per_step_per_gpu": args.cpu_pt_spp,
+                "samples_per_step_per_gpu": args.cpu_pt_width * args.cpu_pt_height * args.cpu_pt_spp,
+                "reference_arm": "unmodified libYafaRay PathIntegrator + yafaray-kdtree-original through its own C API on all host threads; "
+                                 "%dx%d film, %d spp per step" % (args.cpu_pt_width, args.cpu_pt_height, args.cpu_pt_spp)})
     line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": pt_config_dict(args)}
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg}
     r = reference_pt(args)
     if "unavailable" in r:
         line["unavailable"] = r["unavailable"]
@@ -525,28 +587,29 @@ def pt_arm(args, env):
 
     W, H, spp, bounces = args.pt_width, args.pt_height, args.pt_spp, args.pt_bounces
     stream = torch.cuda.Stream(device=dev)
+    # samples per pixel of one step over ALL GPUs: weak scaling keeps `spp` per GPU, strong scaling keeps the pass (spp in total)
+    spp_step = spp if args.scaling == "strong" else spp * world
+    if args.scaling == "strong" and spp % world:
+        raise SystemExit("bench.py: --scaling strong needs --pt-spp divisible by the number of GPUs")
 
-    def make(profile=0):
-        yi = interface.Interface(device=local, shard_index=rank, shard_count=world)
-        scenes_pt.cornell_box(yi, width=W, height=H, spp=spp * world, bounces=bounces, accelerator=ACCELERATOR_TYPE)
+    def make(profile=0, comm=None):
+        yi = interface.Interface(device=local, shard_index=rank, shard_count=world, comm=comm)
+        if args.workload == "c4":
+            scenes_pt.city(yi, n_tri_target=args.city_tris, width=W, height=H, spp=spp_step, bounces=bounces, accelerator=ACCELERATOR_TYPE, filter_type="gauss")
+        else:
+            scenes_pt.cornell_box(yi, width=W, height=H, spp=spp_step, bounces=bounces, accelerator=ACCELERATOR_TYPE)
         yi.render_params["b200_profile"] = profile
         return yi
 
-    # film: [weights | rgba] in ONE tensor so that a pass is combined across GPUs by a single all-reduce
-    pass_film = torch.zeros(H * W * 5, device=dev, dtype=torch.float32)
-    total_film = torch.zeros_like(pass_film) if world > 1 else None
-    yi = make()
-    yi.film_buffers = (pass_film[: H * W], pass_film[H * W:])
+    # N > 1: the product's sharded mode (Interface with a comm): every rank splats into its pass film, ONE NCCL all-reduce of
+    # [weights | rgba] per pass merges the ranks (the film merge is linear), the sum goes into the total film every rank keeps
+    torch.cuda.set_stream(stream)
+    yi = make(comm=dist if world > 1 else None)
     yi.upload()
     yi.accelerator.set_stream(stream.cuda_stream)
 
     def step(k):
-        yi.render_pass(spp * world, k * spp * world, 0)      # this GPU renders the samples s with s mod N == rank
-        if world > 1:
-            with torch.cuda.stream(stream):
-                dist.all_reduce(pass_film)                   # one NCCL sum over NVLink per pass (film merge is linear)
-                total_film.add_(pass_film)
-                pass_film.zero_()
+        yi.render_pass_reduced(spp_step, k * spp_step, 0)      # this GPU renders the samples s with s mod N == rank
 
     for k in range(args.warmup):
         step(k)
@@ -566,11 +629,11 @@ def pt_arm(args, env):
     if sampler:
         sampler.mark(w0, w1)
     total_ms = e0.elapsed_time(e1)
-    launches = yi.accelerator.stats()["kernel_launches"] - launches0 + (3 * args.steps if world > 1 else 0)
+    launches = yi.accelerator.stats()["kernel_launches"] - launches0      # this repo's kernels only (the NCCL all-reduce and the two film adds per pass are library kernels)
     st = yi.pass_stats()
-    film = (total_film if world > 1 else pass_film)
-    wsum = float(film[: H * W].sum())
-    mean_rgb = float((film[H * W:].view(H * W, 4)[:, :3].sum(0) / max(wsum, 1e-30)).mean())
+    fw_, frgba_ = yi.read_film()
+    wsum = float(fw_.sum(dtype=np.float64))
+    mean_rgb = float((frgba_.reshape(-1, 4)[:, :3].sum(0, dtype=np.float64) / max(wsum, 1e-30)).mean())
 
     # ---- end to end: the whole render call with host-side scene + host film (upload, build, pass, D2H film) ----
     e2e = None
@@ -578,14 +641,14 @@ def pt_arm(args, env):
         e_steps = max(1, min(args.steps, 5))
         ye = make()
         ye.upload()
-        ye.render_pass(spp * world, 0, 0)
+        ye.render_pass(spp_step, 0, 0)
         ye.read_film(pinned=True)
         barrier()
         h2d = int(ye._assembled["tris"].nbytes + ye._assembled["flags"].nbytes + 4096)
         t0 = time.perf_counter()
         for k in range(e_steps):
             ye.upload()                                      # host triangles/materials/lights/camera -> device, BVH8 build
-            ye.render_pass(spp * world, k * spp * world, 0)
+            ye.render_pass(spp_step, k * spp_step, 0)
             fw, frgba = ye.read_film(pinned=True)            # device -> host film (weights + rgba), page-locked staging
         barrier()
         e2e = {"ms": (time.perf_counter() - t0) * 1e3, "steps": e_steps, "h2d": h2d, "d2h": int(fw.nbytes + frgba.nbytes)}
@@ -594,7 +657,7 @@ def pt_arm(args, env):
     # ---- one profiled pass: device time per kernel class + BVH visit counters (for the roofline) ----
     yp = make(profile=1)
     yp.upload()
-    yp.render_pass(spp * world, 0, 0)
+    yp.render_pass(spp_step, 0, 0)
     prof = yp.pass_stats()
     yp.clearAll()
 
@@ -605,7 +668,7 @@ def pt_arm(args, env):
     if rank != 0:
         yi.clearAll()
         return None
-    n = W * H * spp                                           # pixel-samples per GPU per step
+    n = W * H * spp_step // world                             # pixel-samples per GPU per step
     value = n * world * args.steps / (total_ms * 1e-3) * 1e-6
     peak, peak_src = load_peaks()
     names = ["camera rays", "trace_closest", "trace_shadow", "path stages (camera hit, start, per-bounce)", "extra light-sample stages", "splat"]
@@ -624,8 +687,8 @@ def pt_arm(args, env):
     traffic, traffic_src = measured_traffic(names[dom], args)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": pt_config_dict(args),
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": pt_config_dict(args, world),
         "rays_per_sample": {"closest": st["rays_closest"] / st["samples"], "shadow": st["rays_shadow"] / st["samples"]},
         "mrays_s": (st["rays_closest"] + st["rays_shadow"]) / st["samples"] * value,
         "film_check": {"weight_sum": wsum, "mean_rgb": mean_rgb},
@@ -690,8 +753,15 @@ def main():
 
     env = {"torch": torch, "dist": dist, "world": world, "rank": rank, "local": local, "dev": dev, "barrier": barrier,
            "sampler": ClockSampler(local) if rank == 0 else None}
-    line = pt_arm(args, env)
-    rb = None if args.no_raybatch else raybatch_arm(args, env)
+    if args.workload == "c5":
+        # the soup has no path-traced part: its ray batches are the line
+        line = raybatch_arm(args, env)
+        if rank == 0:
+            line.update({"higher_is_better": True, "vs_baseline": None, "dtype": "f32", "data": "synthetic"})
+        rb = None
+    else:
+        line = pt_arm(args, env)
+        rb = None if args.no_raybatch else raybatch_arm(args, env)
     if rank == 0:
         if rb is not None:
             line["raybatch"] = rb

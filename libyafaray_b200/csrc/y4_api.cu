@@ -175,7 +175,7 @@ static int slot_acquire(y4gpu_ctx *ctx, Y4TraceSlot **out)
 		if(!ctx->free_slots.empty()) { *out = ctx->free_slots.back(); ctx->free_slots.pop_back(); return Y4GPU_OK; }
 	}
 	Y4TraceSlot *s = new Y4TraceSlot;
-	bool ok = cudaEventCreate(&s->ev0) == cudaSuccess && cudaEventCreate(&s->ev1) == cudaSuccess
+	bool ok = cudaEventCreate(&s->ev0) == cudaSuccess && cudaEventCreate(&s->ev1) == cudaSuccess && cudaEventCreateWithFlags(&s->ev_dep, cudaEventDisableTiming) == cudaSuccess
 		&& cudaMalloc(&s->d_counters, Y4TraceSlot::kMaxChunks * sizeof(unsigned long long)) == cudaSuccess;
 	for(int i = 0; ok && i < Y4TraceSlot::kStreams; ++i)
 		ok = cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking) == cudaSuccess && cudaEventCreateWithFlags(&s->ev_join[i], cudaEventDisableTiming) == cudaSuccess;
@@ -203,6 +203,7 @@ static void slot_free_all(y4gpu_ctx *ctx)
 		}
 		if(s->ev0) cudaEventDestroy(s->ev0);
 		if(s->ev1) cudaEventDestroy(s->ev1);
+		if(s->ev_dep) cudaEventDestroy(s->ev_dep);
 		cudaFree(s->d_rays); cudaFree(s->d_hits); cudaFree(s->d_counters); cudaFree(s->d_mat_transp);
 		if(s->h_pinned) cudaFreeHost(s->h_pinned);
 		delete s;
@@ -262,6 +263,12 @@ static int trace_host(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t 
 		n_chunks = (n + chunk - 1) / chunk;
 	}
 	cudaStream_t s0 = s->streams[0];
+	if(ctx->stream != ctx->own_stream)
+	{
+		// a caller-installed stream: whatever it queued before this call (e.g. an asynchronous copy into the ray buffer) comes first
+		Y4_SLOT_CUDA(ctx, cudaEventRecord(s->ev_dep, ctx->stream));
+		Y4_SLOT_CUDA(ctx, cudaStreamWaitEvent(s0, s->ev_dep, 0));
+	}
 	Y4_SLOT_CUDA(ctx, cudaMemsetAsync(s->d_counters, 0, n_chunks * sizeof(unsigned long long), s0));
 	Y4_SLOT_CUDA(ctx, cudaEventRecord(s->ev0, s0));
 	const int n_streams = n_chunks > 1 ? Y4TraceSlot::kStreams : 1;
@@ -323,9 +330,8 @@ static int trace_impl(y4gpu_ctx *ctx, int kind, bool counted, const y4gpu_ray *r
 	if(n == 0) return Y4GPU_OK;
 	if(cudaSetDevice(ctx->device) != cudaSuccess) { slot_error(ctx, "cudaSetDevice failed"); return Y4GPU_ERR_CUDA; }
 	const bool rays_dev = is_device_ptr(rays), out_dev = is_device_ptr(out);
-	// host buffers on both sides, and the context runs on its own stream (a caller-installed stream orders the work against
-	// the caller's: keep it on that stream): the re-entrant path
-	if(!rays_dev && !out_dev && !counted && ctx->stream == ctx->own_stream)
+	// host buffers on both sides: the re-entrant path (synchronous; ordered after the work already queued on a caller-installed stream)
+	if(!rays_dev && !out_dev && !counted)
 		return trace_host(ctx, kind, rays, n, out, sizeof(Y4Hit), 0, nullptr, 0, false);
 	std::lock_guard<std::mutex> lock(ctx->mtx);
 	if(!rays_dev || !out_dev) { const int rc = ensure_stage(ctx, n, sizeof(Y4Hit)); if(rc) return rc; }
@@ -362,7 +368,7 @@ static int tshadow_impl(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int m
 	if(n == 0) return Y4GPU_OK;
 	if(cudaSetDevice(ctx->device) != cudaSuccess) { slot_error(ctx, "cudaSetDevice failed"); return Y4GPU_ERR_CUDA; }
 	const bool rays_dev = is_device_ptr(rays), out_dev = is_device_ptr(out);
-	if(!rays_dev && !out_dev && ctx->stream == ctx->own_stream)
+	if(!rays_dev && !out_dev)
 		return trace_host(ctx, Y4_TRACE_TSHADOW, rays, n, out, sizeof(y4gpu_tshit), max_depth, mat_transparency, n_mat, inner);
 	std::lock_guard<std::mutex> lock(ctx->mtx);
 	if(!rays_dev || !out_dev) { const int rc = ensure_stage(ctx, n, sizeof(y4gpu_tshit)); if(rc) return rc; }

@@ -16,7 +16,7 @@ struct Y4TraceSlot
 {
 	static constexpr int kStreams = 4, kMaxChunks = 64;
 	cudaStream_t streams[kStreams] = {nullptr, nullptr, nullptr, nullptr};
-	cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_join[kStreams] = {nullptr, nullptr, nullptr, nullptr};
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_dep = nullptr, ev_join[kStreams] = {nullptr, nullptr, nullptr, nullptr};
 	Y4Ray *d_rays = nullptr; void *d_hits = nullptr;
 	uint64_t cap_rays = 0, cap_hit_bytes = 0;
 	unsigned long long *d_counters = nullptr;        // kMaxChunks work counters

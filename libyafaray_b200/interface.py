@@ -47,8 +47,14 @@ class _Mesh:
 class Interface:
     """`yafaray_Interface_t` for the GPU back end: build a scene with the C API's calls, then render()."""
 
-    def __init__(self, device: int = 0, shard_index: int = 0, shard_count: int = 1):
+    def __init__(self, device: int = 0, shard_index: int = 0, shard_count: int = 1, comm=None):
+        """comm: multi-GPU rendering (one process per GPU): an object with `all_reduce(tensor)` summing a CUDA tensor over the
+        shard_count ranks in place -- `torch.distributed` after init_process_group("nccl") is one.  With a comm, render() /
+        render_pass_reduced() combine the ranks' pass films with ONE all-reduce per AA pass (the linear film merge of
+        imagefilm.cc:940-1018) and every rank ends up with the complete film; see Interface.distributed()."""
         self.device, self.shard_index, self.shard_count = device, shard_index, shard_count
+        self.comm = comm
+        self._pass_film = self._total_film = None   # sharded mode: [weights | rgba] CUDA tensors (this pass / all passes, all ranks)
         self.params: Dict[str, object] = {}
         self.eparams: List[Dict[str, object]] = []     # the ParamMap list of paramsPushList (shader nodes)
         self._cparams = self.params
@@ -72,6 +78,18 @@ class Interface:
         self.film_buffers = None  # optional (weights, rgba) torch CUDA tensors installed by the caller
         self._pinned_film = None
         self.last_stats: dict = {}
+
+    @classmethod
+    def distributed(cls):
+        """One Interface per rank of an initialised torch.distributed NCCL job (torchrun): GPU = LOCAL_RANK, shard = RANK of
+        WORLD_SIZE.  Every rank builds the same scene (the scene and its BVH8 are replicated)."""
+        import os
+
+        import torch.distributed as dist
+
+        if not dist.is_initialized():
+            raise Y4Error("Interface.distributed() needs torch.distributed.init_process_group('nccl') first")
+        return cls(device=int(os.environ.get("LOCAL_RANK", "0")), shard_index=dist.get_rank(), shard_count=dist.get_world_size(), comm=dist)
 
     # ---- the "current ParamMap" (interface.cc:118-181) -------------------------------------------
     def paramsClearAll(self):
@@ -637,11 +655,41 @@ class Interface:
         uptr = C.c_void_p(a["tri_uv"].ctypes.data) if a["tri_uv"] is not None else None
         _lib.check(ctx, L.y4gpu_pt_set_textures(ctx, a["textures"], a["n_tex"], a["layers"], a["n_layers"], optr, uptr), "y4gpu_pt_set_textures")
         _lib.check(ctx, L.y4gpu_pt_set_scene(ctx, C.byref(a["cam"]), a["mats"], a["n_mat"], a["lights"], a["n_light"], C.byref(a["params"]), nptr), "y4gpu_pt_set_scene")
+        if self.comm is not None and self.shard_count > 1:
+            # sharded rendering: this rank splats into its pass film, which is the collective's buffer; the all-reduced passes
+            # are summed into the total film every rank keeps (noise detection and read-back work on that)
+            import torch
+
+            npx = a["params"].width * a["params"].height
+            dev = torch.device("cuda", self.device)
+            if self._pass_film is None or self._pass_film.numel() != 5 * npx:
+                self._pass_film = torch.zeros(5 * npx, device=dev, dtype=torch.float32)
+                self._total_film = torch.zeros(5 * npx, device=dev, dtype=torch.float32)
+            self.film_buffers = (self._pass_film[:npx], self._pass_film[npx:])
+            self.accelerator.set_stream(torch.cuda.current_stream(dev).cuda_stream)     # kernels, collective and adds on one stream
         if self.film_buffers is not None:
             w, rgba = self.film_buffers
             _lib.check(ctx, L.y4gpu_pt_set_film_buffers(ctx, C.c_void_p(w.data_ptr()), C.c_void_p(rgba.data_ptr())), "y4gpu_pt_set_film_buffers")
         self._assembled = a
         return a
+
+    @property
+    def sharded(self) -> bool:
+        return self._total_film is not None and self.comm is not None and self.shard_count > 1
+
+    def reduce_pass(self):
+        """Sharded mode: sum this pass over the ranks (one all-reduce of [weights | rgba], 20 B / pixel, over NVLink) and add it
+        to the total film.  Queued on the stream the pass ran on; nothing is synchronised."""
+        if not self.sharded:
+            return
+        self.comm.all_reduce(self._pass_film)
+        self._total_film.add_(self._pass_film)
+        self._pass_film.zero_()
+
+    def render_pass_reduced(self, n_samples: int, offset: int, aa_pass: int, pixel_list=None):
+        """render_pass on this rank's shard of the samples + reduce_pass: afterwards every rank holds the complete film."""
+        self.render_pass(n_samples, offset, aa_pass, pixel_list=pixel_list)
+        self.reduce_pass()
 
     def render_pass(self, n_samples: int, offset: int, aa_pass: int, pixel_list=None):
         """TiledIntegrator::renderPass(samples, offset, adaptive, aa_pass_number) on this GPU's shard."""
@@ -674,6 +722,9 @@ class Interface:
         film: optional (weights, rgba) torch CUDA tensors holding the accumulated film (multi-GPU: the all-reduced total)."""
         L, ctx = self.accelerator._L, self.accelerator.ctx
         ptr, n = C.c_void_p(), C.c_uint64()
+        if film is None and self.sharded:          # the all-reduced total: identical on every rank, so are the flagged pixels
+            npx = self._total_film.numel() // 5
+            film = (self._total_film[:npx], self._total_film[npx:])
         fw = C.c_void_p(film[0].data_ptr()) if film is not None else None
         fr = C.c_void_p(film[1].data_ptr()) if film is not None else None
         _lib.check(ctx, L.y4gpu_pt_next_pass(ctx, C.byref(aa), fw, fr, C.byref(ptr), C.byref(n)), "y4gpu_pt_next_pass")
@@ -701,13 +752,17 @@ class Interface:
         f32 = np.float32
         L, ctx = self.accelerator._L, self.accelerator.ctx
         _lib.check(ctx, L.y4gpu_pt_clear_film(ctx), "y4gpu_pt_clear_film")
+        if self.sharded:
+            if mode != "none":
+                raise Y4Error("film_load_save_mode together with multi-GPU sharding is not supported (save the film from rank 0's read_film())")
+            self._total_film.zero_()
         stats = {"samples": 0, "rays_closest": 0, "rays_shadow": 0, "kernel_launches": 0, "pass_ms": 0.0}
         self.resumed = resumed is not None
         if resumed is not None:                                 # renderPass(0, film sampling offset): nothing is rendered
             _lib.check(ctx, L.y4gpu_pt_write_film(ctx, C.c_void_p(resumed[0].ctypes.data), C.c_void_p(resumed[1].ctypes.data)), "y4gpu_pt_write_film")
             self.sampling_offset = resumed[2]
         else:
-            self.render_pass(pr.aa_samples, 0, 0)
+            self.render_pass_reduced(pr.aa_samples, 0, 0)
             self._add_stats(stats)
             self.sampling_offset = pr.aa_samples
         threshold = f32(rp.get("AA_threshold", 0.05))
@@ -729,7 +784,7 @@ class Interface:
             self.resampled_per_pass.append(0 if skip else resampled)
             n = int(np.ceil(f32(pr.aa_inc_samples) * mult))
             if not skip and resampled > 0:
-                self.render_pass(n, acum, i, pixel_list=plist)
+                self.render_pass_reduced(n, acum, i, pixel_list=plist)
                 self._add_stats(stats)
                 self.sampling_offset = acum + n                # ImageFilm::setSamplingOffset(offset + samples)
             acum += n
@@ -773,6 +828,13 @@ class Interface:
             w = np.empty((pr.height, pr.width), np.float32)
             rgba = np.empty((pr.height, pr.width, 4), np.float32)
         L, ctx = self.accelerator._L, self.accelerator.ctx
+        if self.sharded:                            # the complete film (all passes, all ranks) lives in the total tensor
+            import torch
+
+            npx = pr.height * pr.width
+            torch.from_numpy(w.reshape(-1)).copy_(self._total_film[:npx])
+            torch.from_numpy(rgba.reshape(-1)).copy_(self._total_film[npx:])
+            return w, rgba
         _lib.check(ctx, L.y4gpu_pt_read_film(ctx, C.c_void_p(w.ctypes.data), C.c_void_p(rgba.ctypes.data)), "y4gpu_pt_read_film")
         return w, rgba
 

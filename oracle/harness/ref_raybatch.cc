@@ -7,7 +7,9 @@
 //   Accelerator::intersect(ray, t_max)       (src/accelerator/accelerator_kdtree.cc:634-773)
 //   Accelerator::isShadowed(ray, bias)       (src/accelerator/accelerator.cc:69-80 -> intersectS :775-904)
 //
-// usage: ref_raybatch <tris.f32> <rays.f32> <closest|shadow> <hits.out> [threads] [accel_type]
+//   Accelerator::isShadowed(ray, depth, bias, cam) (src/accelerator/accelerator.cc:82-94 -> intersectTs :911-1061)
+//
+// usage: ref_raybatch <tris.f32> <rays.f32> <closest|shadow|tshadow> <hits.out> [threads] [accel_type]
 //        ref_raybatch <tris.f32> --serve - - [threads] [accel_type]
 //          serve mode: builds the kd-tree once, prints one JSON line, then answers each stdin line
 //          "<closest|shadow> <rays.f32> <hits.out> [repeats]" with one JSON timing line (used by bench.py's CPU legs)
@@ -16,6 +18,10 @@
 //   hits.out : n_ray * {float t, float bu, float bv, int32 prim}; prim = -1 on miss.
 //              (bu,bv) = Moller-Trumbore (u',v') == reference barycentric_v_/barycentric_w_
 //              closest: t = hit distance; shadow: t = 0, prim = first blocker found.
+//              tshadow: (t, bu, bv) = the filter colour (r, g, b) of the transparent blockers, prim = blocker when shadowed.
+//   tshadow needs materials: environment REF_RAYBATCH_MATS = text file, one shinydiffusemat per line
+//              "transparency r g b transmit_filter"; REF_RAYBATCH_TRIMAT = int32 material index per triangle;
+//              REF_RAYBATCH_TS_DEPTH = max_depth (default 4).
 // Prints one JSON line with build and trace timings.
 #include "scene/scene.h"
 #include "accelerator/accelerator.h"
@@ -25,6 +31,9 @@
 #include "geometry/bound.h"
 #include "geometry/object/object.h"
 #include "geometry/primitive/primitive.h"
+#include "material/material.h"
+#include "color/color.h"
+#include <tuple>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -62,7 +71,7 @@ int main(int argc, char **argv)
 	const size_t n_tri = tris.size() / 9;
 
 	Logger logger(nullptr, nullptr, YAFARAY_DISPLAY_CONSOLE_HIDDEN);
-	logger.setConsoleMasterVerbosity(YAFARAY_LOG_LEVEL_MUTE);
+	logger.setConsoleMasterVerbosity(getenv("REF_RAYBATCH_VERBOSE") ? YAFARAY_LOG_LEVEL_VERBOSE : YAFARAY_LOG_LEVEL_MUTE);
 	logger.setLogMasterVerbosity(YAFARAY_LOG_LEVEL_MUTE);
 	Scene scene(logger);
 	scene.startObjects();
@@ -70,10 +79,42 @@ int main(int argc, char **argv)
 	op["type"] = std::string("mesh");
 	op["num_vertices"] = (int) (n_tri * 3);
 	op["num_faces"] = (int) n_tri;
+	// optional materials (transparent-shadow batches)
+	std::vector<const std::unique_ptr<const Material> *> mats;
+	std::vector<int32_t> tri_mat;
+	if(const char *mf = getenv("REF_RAYBATCH_MATS"))
+	{
+		FILE *f = fopen(mf, "r");
+		if(!f) { fprintf(stderr, "cannot open %s\n", mf); return 2; }
+		float tr, r, g, b, tf;
+		while(fscanf(f, "%f %f %f %f %f", &tr, &r, &g, &b, &tf) == 5)
+		{
+			ParamMap mp;
+			mp["type"] = std::string("shinydiffusemat");
+			mp["color"] = Rgba(r, g, b, 1.f);
+			mp["transparency"] = tr;
+			mp["transmit_filter"] = tf;
+			const std::string name = "m" + std::to_string(mats.size());
+			mats.push_back(scene.createMaterial(name, mp, {}));
+			if(!mats.back()) { fprintf(stderr, "createMaterial failed\n"); return 3; }
+		}
+		fclose(f);
+		const char *tf_path = getenv("REF_RAYBATCH_TRIMAT");
+		if(!tf_path) { fprintf(stderr, "REF_RAYBATCH_TRIMAT missing\n"); return 2; }
+		FILE *g2 = fopen(tf_path, "rb");
+		tri_mat.resize(n_tri);
+		if(!g2 || fread(tri_mat.data(), 4, n_tri, g2) != n_tri) { fprintf(stderr, "short read %s\n", tf_path); return 2; }
+		fclose(g2);
+	}
+	const int ts_depth = getenv("REF_RAYBATCH_TS_DEPTH") ? atoi(getenv("REF_RAYBATCH_TS_DEPTH")) : 4;
 	Object *obj = scene.createObject("s", op);
 	if(!obj) { fprintf(stderr, "createObject failed\n"); return 3; }
 	for(size_t i = 0; i < n_tri * 3; ++i) scene.addVertex({tris[3 * i], tris[3 * i + 1], tris[3 * i + 2]});
-	for(size_t i = 0; i < n_tri; ++i) scene.addFace({(int) (3 * i), (int) (3 * i + 1), (int) (3 * i + 2)});
+	for(size_t i = 0; i < n_tri; ++i)
+	{
+		if(!tri_mat.empty()) scene.setCurrentMaterial(mats.at(tri_mat[i]));
+		scene.addFace({(int) (3 * i), (int) (3 * i + 1), (int) (3 * i + 2)});
+	}
 	scene.endObject();
 	scene.endObjects();
 
@@ -93,8 +134,9 @@ int main(int argc, char **argv)
 	const double build_s = std::chrono::duration<double>(t1 - t0).count();
 
 	// traces one batch with n_threads host threads; returns seconds
-	auto trace = [&](const std::vector<float> &rays, bool shadow, std::vector<HitRec> &out) -> double
+	auto trace = [&](const std::vector<float> &rays, int mode /* 0 closest, 1 shadow, 2 transparent shadow */, std::vector<HitRec> &out) -> double
 	{
+		const bool shadow = mode == 1;
 		const size_t n_ray = rays.size() / 8;
 		out.resize(n_ray);
 		auto worker = [&](int tid)
@@ -109,7 +151,14 @@ int main(int argc, char **argv)
 					const float *r = &rays[8 * i];
 					Ray ray({r[0], r[1], r[2]}, {r[4], r[5], r[6]}, r[3], r[7]);
 					HitRec h{0.f, 0.f, 0.f, -1};
-					if(shadow)
+					if(mode == 2)
+					{
+						const auto res = accel->isShadowed(ray, ts_depth, 0.f, nullptr);
+						const Rgb c = std::get<1>(res);
+						h.t = c.r_; h.bu = c.g_; h.bv = c.b_;
+						if(std::get<0>(res)) h.prim = std::get<2>(res) ? index_of[std::get<2>(res)] : -2;
+					}
+					else if(shadow)
 					{
 						const auto res = accel->isShadowed(ray, 0.f);
 						if(res.first) h.prim = res.second ? index_of[res.second] : -2;
@@ -158,10 +207,10 @@ int main(int argc, char **argv)
 	if(!serve)
 	{
 		const std::vector<float> rays = readFloats(argv[2]);
-		const bool shadow = strcmp(argv[3], "shadow") == 0;
-		const double trace_s = trace(rays, shadow, out);
+		const int mode = strcmp(argv[3], "tshadow") == 0 ? 2 : (strcmp(argv[3], "shadow") == 0 ? 1 : 0);
+		const double trace_s = trace(rays, mode, out);
 		if(!writeHits(argv[4], out)) return 2;
-		report(shadow ? "shadow" : "closest", rays.size() / 8, out, trace_s, 1);
+		report(argv[3], rays.size() / 8, out, trace_s, 1);
 		return 0;
 	}
 	report("build", 0, out, 0., 0);
@@ -174,12 +223,12 @@ int main(int argc, char **argv)
 		if(got < 3) break;
 		if(repeats < 1) repeats = 1;
 		const std::vector<float> rays = readFloats(rays_path);
-		const bool shadow = strcmp(kind, "shadow") == 0;
+		const int mode = strcmp(kind, "tshadow") == 0 ? 2 : (strcmp(kind, "shadow") == 0 ? 1 : 0);
 		double best = 1e30;   // serve mode reports the mean over repeats in trace_s
 		double sum = 0.;
-		for(int r = 0; r < repeats; ++r) { const double s = trace(rays, shadow, out); sum += s; if(s < best) best = s; }
+		for(int r = 0; r < repeats; ++r) { const double s = trace(rays, mode, out); sum += s; if(s < best) best = s; }
 		if(!writeHits(out_path, out)) return 2;
-		report(shadow ? "shadow" : "closest", rays.size() / 8, out, sum / repeats, repeats);
+		report(kind, rays.size() / 8, out, sum / repeats, repeats);
 	}
 	return 0;
 }

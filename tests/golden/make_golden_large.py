@@ -1,0 +1,86 @@
+#!/usr/bin/env python3
+"""TEST INFRASTRUCTURE: golden vectors for the full-size configurations, generated HERE (where /root/reference exists) by the
+UNMODIFIED reference (oracle/_ref), committed so that the GPU box can check them without the reference tree.
+
+  rays_soup5m.npz   <- BASELINE config C5 as SURVEY.md 8(d) prescribes it for the oracle: the first 5 000 000 triangles of the
+                       50 M-triangle soup (identical generator, scenes.triangle_soup), 65 536 incoherent closest-hit rays and
+                       65 536 segment (any-hit) rays against yafaray-kdtree-original
+  pt_city_large.npz <- BASELINE config C4 at a size the reference renders in minutes: the instanced city (scenes_pt.city) with
+                       >= 200 000 instanced triangles at 240 x 135, 8 bounces + NEE, reference PathIntegrator in the deterministic
+                       mode (threads = 1, linear tiles, RR off)
+
+  pt_rr.npz         <- Cornell box with the integrator's default Russian roulette (russian_roulette_min_bounces = 0), 1024 spp
+
+Run from the repo root:  python tests/golden/make_golden_large.py [soup|city]
+"""
+import os
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import helpers  # noqa: E402
+from libyafaray_b200 import scenes, scenes_pt  # noqa: E402
+
+SOUP5M = dict(n_tri=5_000_000, n_rays=65536)
+SOUP50M = dict(n_tri=50_000_000, n_rays=65536)      # C5 at FULL size (needs ~30 GB of host memory and ~10 min for the kd-tree)
+CITY1M = dict(scene="city", n_tri_target=1_000_000, n_base=32, grid=48, tri_range=(1000, 8000), width=480, height=270, spp=2, bounces=8, filter_type="gauss")
+CITY200K = dict(scene="city", n_tri_target=200_000, n_base=16, grid=24, tri_range=(500, 4000), width=240, height=135, spp=2, bounces=8, filter_type="gauss")
+
+
+def make_soup(cfg=SOUP5M, name="rays_soup5m.npz"):
+    t0 = time.time()
+    SOUP5M = cfg
+    tris = np.concatenate([scenes.triangle_soup(min(5_000_000, cfg["n_tri"] - f), first=f) for f in range(0, cfg["n_tri"], 5_000_000)])
+    inc, seg = scenes.incoherent_rays(SOUP5M["n_rays"]), scenes.segment_rays(SOUP5M["n_rays"])
+    with helpers.RefServer(tris, threads=0) as srv:
+        print("kd-tree built in %.1f s" % srv.info["build_s"], flush=True)
+        h_inc, _ = srv.trace(inc, "closest")
+        h_seg, _ = srv.trace(seg, "shadow")
+        bound = np.array(srv.info["bound"], np.float32)
+    # rays are regenerated from their seeds by the test (scenes.incoherent_rays / segment_rays): only the hit records are stored
+    np.savez_compressed(os.path.join(HERE, name), scene=np.array([SOUP5M["n_tri"], SOUP5M["n_rays"]]),
+                        hit_incoherent=h_inc, occluded_segment=np.packbits(h_seg["prim"] != -1), bound=bound)
+    print(name + ": %d / %d incoherent hits, %d occluded segments, %.0f s" % ((h_inc["prim"] >= 0).sum(), len(inc), (h_seg["prim"] != -1).sum(), time.time() - t0))
+
+
+def make_city():
+    out = {}
+    for key, cfg in (("city200k", CITY200K), ("city1m", CITY1M)):
+        t0 = time.time()
+        rec = helpers.ScriptRecorder()
+        scenes_pt.build(rec, **cfg)
+        img, info = helpers.ref_render(rec)
+        out[key] = img.astype(np.float32)
+        print("%s: %s, reference render %.1f s, total %.0f s" % (key, img.shape, info["render_s"], time.time() - t0), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_city_large.npz"), **out)
+
+
+RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
+
+
+def make_rr():
+    """Russian roulette draws from a rand()-seeded generator in the reference (integrator_tiled.cc:272) and from a per-path hash
+    on the device: not sample-exact by construction, so the golden is a converged image (1024 spp) for a statistical test."""
+    t0 = time.time()
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, threads=8, **RR_ON)
+    img, info = helpers.ref_render(rec)
+    np.savez_compressed(os.path.join(HERE, "pt_rr.npz"), rr_on=img.astype(np.float32))
+    print("pt_rr.npz: %s, reference render %.1f s, total %.0f s" % (img.shape, info["render_s"], time.time() - t0))
+
+
+if __name__ == "__main__":
+    what = sys.argv[1:] or ["soup", "city", "rr"]
+    if "city" in what:
+        make_city()
+    if "soup" in what:
+        make_soup()
+    if "rr" in what:
+        make_rr()
+    if "soup50m" in what:
+        make_soup(SOUP50M, "rays_soup50m.npz")

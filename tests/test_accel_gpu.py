@@ -211,3 +211,129 @@ def test_many_scale_chain_scene_deep_tree_stack_bound():
     assert r["bad"] == 0 and r["t_out_of_tol"] == 0 and r["near_tie"] <= 16 and r["same"] >= n - 16, r
     assert np.array_equal(acc.isShadowed(rays)["prim"] >= 0, helpers.emu_brute(tris, rays, 1)["prim"] >= 0)
     acc.close()
+
+
+# ---- full-size configurations against the reference (pin C3 / C5 / intersectTs) ------------------------------------
+@pytest.mark.skipif(not helpers.have_ref(), reason="oracle/_ref not built")
+def test_full_size_c3_vs_live_reference_kdtree():
+    """BASELINE config C3 at FULL size: the 1 000 000-triangle displaced sphere; 3 x 262 144 rays (primary / shadow / cosine-diffuse)
+    against yafaray-kdtree-original built on the same triangles by the unmodified reference (oracle/_ref, live on this box)."""
+    from libyafaray_b200.accelerator import AcceleratorB200
+    tris = scenes.displaced_sphere(1000, 500)
+    assert len(tris) == 1_000_000
+    acc = AcceleratorB200(tris)
+    with helpers.RefServer(tris, threads=0) as srv:
+        prim = scenes.primary_rays(512, 512)
+        h_ref, _ = srv.trace(prim, "closest")
+        got = acc.intersect(prim)
+        r = helpers.compare_closest(got, h_ref)
+        assert r["bad"] == 0 and r["t_out_of_tol"] == 0 and r["uv_out_of_tol"] == 0 and r["near_tie"] <= 8 and r["bit_exact_t"] == r["n_hit_both"], r
+        assert r["n_hit_both"] > 100_000
+        p, nrm, ok = scenes.hit_points_normals(tris, prim, h_ref["t"], h_ref["prim"])
+        sh, df = scenes.shadow_rays(p, ok), scenes.diffuse_rays(p, nrm, ok)
+        h_sh, _ = srv.trace(sh, "shadow")
+        assert np.array_equal(acc.isShadowed(sh)["prim"] >= 0, h_sh["prim"] != -1)
+        h_df, _ = srv.trace(df, "closest")
+        r = helpers.compare_closest(acc.intersect(df), h_df)
+        assert r["bad"] == 0 and r["t_out_of_tol"] == 0 and r["uv_out_of_tol"] == 0 and r["near_tie"] <= 8 and r["bit_exact_t"] == r["n_hit_both"], r
+        assert np.array_equal(acc.getBound(), np.array(srv.info["bound"], np.float32))
+    acc.close()
+
+
+@pytest.mark.parametrize("name", ["rays_soup5m.npz", "rays_soup50m.npz"])
+def test_c5_soup_vs_reference_kdtree_golden(name):
+    """BASELINE config C5: the random triangle soup -- its first 5 M triangles (the oracle subsample SURVEY.md 8(d) prescribes)
+    and all 50 M (full size) -- 65 536 incoherent closest-hit rays and 65 536 any-hit segments against the committed hit records
+    of yafaray-kdtree-original (tests/golden/make_golden_large.py)."""
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name)
+    if not os.path.exists(path):
+        pytest.skip(name + " not generated")
+    from libyafaray_b200.accelerator import AcceleratorB200
+    d = np.load(path)
+    n_tri, n_rays = int(d["scene"][0]), int(d["scene"][1])
+    tris = np.concatenate([scenes.triangle_soup(min(5_000_000, n_tri - f), first=f) for f in range(0, n_tri, 5_000_000)])
+    acc = AcceleratorB200(tris)
+    inc, seg = scenes.incoherent_rays(n_rays), scenes.segment_rays(n_rays)
+    r = helpers.compare_closest(acc.intersect(inc), d["hit_incoherent"])
+    assert r["bad"] == 0 and r["t_out_of_tol"] == 0 and r["uv_out_of_tol"] == 0 and r["near_tie"] <= 8 and r["bit_exact_t"] == r["n_hit_both"], r
+    assert r["n_hit_both"] > n_rays // 2
+    occ = np.unpackbits(d["occluded_segment"])[:n_rays].astype(bool)
+    assert np.array_equal(acc.isShadowed(seg)["prim"] >= 0, occ)
+    assert np.array_equal(acc.getBound(), d["bound"])
+    acc.close()
+
+
+def _sheet_scene(rng, n_sheets=12):
+    """Stacked sheets (2 triangles each) across the unit square at increasing z; random materials: several transparent
+    shinydiffuse filters and a few opaque ones."""
+    tris, tri_mat = [], []
+    mats = [(0.0, 0.8, 0.8, 0.8, 1.0)]                         # material 0: opaque
+    for k in range(5):
+        mats.append((float(np.float32(0.3 + 0.13 * k)), *(float(np.float32(c)) for c in rng.random(3)), float(np.float32(0.2 + 0.15 * k))))
+    for s in range(n_sheets):
+        z = 0.1 + 0.07 * s
+        x0, y0 = rng.random(2) * 0.4 - 0.2
+        a, b, c, e = (x0, y0, z), (x0 + 1.0, y0, z + 0.01), (x0 + 1.0, y0 + 1.0, z), (x0, y0 + 1.0, z + 0.01)
+        tris += [[*a, *b, *c], [*a, *c, *e]]
+        m = int(rng.integers(1, len(mats))) if s % 5 != 4 else 0
+        tri_mat += [m, m]
+    return np.array(tris, np.float32), np.array(tri_mat, np.int32), mats
+
+
+@pytest.mark.skipif(not helpers.have_ref(), reason="oracle/_ref not built")
+def test_transparent_shadows_vs_reference_intersectTs(tmp_path):
+    """y4gpu_trace_tshadow against Accelerator::isShadowed(ray, depth, bias, camera) -> AcceleratorKdTree::intersectTs of the
+    unmodified reference on a scene of transparent shinydiffuse sheets: shadowed flag, filter colour product, depth limit."""
+    import os
+    import subprocess
+    from libyafaray_b200 import _lib
+    from libyafaray_b200.accelerator import AcceleratorB200
+    rng = np.random.default_rng(11)
+    tris, tri_mat, mats = _sheet_scene(rng)
+    n = 20000
+    o = np.stack([rng.random(n) * 1.2 - 0.1, rng.random(n) * 1.2 - 0.1, np.zeros(n)], -1)
+    e = np.stack([rng.random(n) * 1.2 - 0.1, rng.random(n) * 1.2 - 0.1, rng.random(n) * 1.1 + 0.05], -1)   # end points inside the stack
+    d = e - o
+    dist = np.linalg.norm(d, axis=1)
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, 0:3] = o; rays[:, 4:7] = d / dist[:, None]; rays[:, 3] = 5e-4; rays[:, 7] = dist
+    rays[: n // 10, 7] = -1.0                                   # some unbounded rays
+    mf, tf = tmp_path / "mats.txt", tmp_path / "trimat.i32"
+    mf.write_text("".join("%r %r %r %r %r\n" % m for m in mats))
+    tri_mat.tofile(tf)
+    f32 = np.float32
+    # Material::getTransparency of an untextured shinydiffusemat (material_shiny_diffuse.cc:442-465)
+    mt = np.array([[f32(f32(m[0]) * f32(f32(m[4]) * f32(m[1 + c]) + f32(f32(1.0) - f32(m[4])))) for c in range(3)] for m in mats], f32)
+    flags = ((tri_mat.astype(np.uint32) << _lib.TRI_MAT_SHIFT) | 7 | np.where(np.array([mats[m][0] for m in tri_mat]) > 1e-5, _lib.TRI_TRANSPARENT, 0)).astype(np.uint32)
+    acc = AcceleratorB200(tris, flags=flags)
+    for depth in (2, 4, 16):
+        with helpers.tempfile.TemporaryDirectory() as dd:
+            tp, rp, hp = (os.path.join(dd, x) for x in ("t.f32", "r.f32", "h.bin"))
+            tris.tofile(tp); rays.tofile(rp)
+            env = dict(os.environ, REF_RAYBATCH_MATS=str(mf), REF_RAYBATCH_TRIMAT=str(tf), REF_RAYBATCH_TS_DEPTH=str(depth))
+            subprocess.run([os.path.join(helpers.REF_DIR, "ref_raybatch"), tp, rp, "tshadow", hp, "4"], check=True, capture_output=True, env=env)
+            ref = np.fromfile(hp, helpers.HIT_DTYPE)
+        got = acc.isShadowedTransparent(rays, depth, mt)
+        shadowed_ref = ref["prim"] != -1
+        assert np.array_equal(got["prim"] >= 0, shadowed_ref), depth
+        assert 0.05 < shadowed_ref.mean() < 0.95
+        lit = ~shadowed_ref
+        col_ref = np.stack([ref["t"], ref["bu"], ref["bv"]], -1)[lit]
+        col = got["filter"][lit]
+        assert (col_ref < 0.999).any(axis=1).mean() > 0.3           # many rays really cross transparent sheets
+        assert np.allclose(col, col_ref, rtol=4e-6, atol=1e-9), float(np.abs(col - col_ref).max())   # products in another order: a few ulp
+    # the compiled plug-in (AcceleratorB200::intersectTs inside libYafaRay), when built: same answers from the reference's own wrapper
+    if helpers.have_plugin("b200_raybatch"):
+        with helpers.tempfile.TemporaryDirectory() as dd:
+            tp, rp, hp = (os.path.join(dd, x) for x in ("t.f32", "r.f32", "h.bin"))
+            tris.tofile(tp); rays.tofile(rp)
+            env = dict(os.environ, REF_RAYBATCH_MATS=str(mf), REF_RAYBATCH_TRIMAT=str(tf), REF_RAYBATCH_TS_DEPTH="4")
+            subprocess.run([os.path.join(helpers.B200_DIR, "b200_raybatch"), tp, rp, "tshadow", hp, "8", "yafaray-b200-bvh8"], check=True, capture_output=True, env=env)
+            plug = np.fromfile(hp, helpers.HIT_DTYPE)
+            subprocess.run([os.path.join(helpers.REF_DIR, "ref_raybatch"), tp, rp, "tshadow", hp, "4"], check=True, capture_output=True, env=env)
+            ref = np.fromfile(hp, helpers.HIT_DTYPE)
+        assert np.array_equal(plug["prim"] != -1, ref["prim"] != -1)
+        lit = ref["prim"] == -1
+        assert np.allclose(np.stack([plug["t"], plug["bu"], plug["bv"]], -1)[lit], np.stack([ref["t"], ref["bu"], ref["bv"]], -1)[lit], rtol=4e-6, atol=1e-9)
+    acc.close()

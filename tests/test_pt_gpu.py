@@ -212,3 +212,40 @@ def test_film_save_and_load_save_resume(tmp_path):
     assert more.resumed and more.last_stats["samples"] == 64 * 36 * 3
     assert (w3 >= w1).all() and 2.2 < float(w3.sum()) / float(w1.sum()) < 3.2 and np.isfinite(c3).all()   # 2 + 3 samples per pixel; the filter footprint varies with the jitter
     assert film_io.load_film(film_io.film_path(path, 0), 64, 36)["sampling_offset"] == 5
+
+
+sys.path.insert(0, GOLD)
+from make_golden_large import CITY1M, CITY200K, RR_ON  # noqa: E402
+
+
+@pytest.mark.parametrize("key,cfg", [("city200k", CITY200K), ("city1m", CITY1M)])
+def test_c4_instanced_city_vs_reference_golden(key, cfg):
+    """BASELINE config C4 at sizes the reference renders in seconds: 200 k and 1 M instanced triangles (yafaray_addInstance),
+    8 bounces + NEE, against the committed reference PathIntegrator renders (tests/golden/make_golden_large.py)."""
+    ref = np.load(os.path.join(GOLD, "pt_city_large.npz"))[key]
+    yi = _gpu(**cfg)
+    img = yi.render()
+    assert yi._assembled["tris"].shape[0] >= 0.95 * cfg["n_tri_target"]
+    assert helpers.psnr(img, ref) >= PSNR_MIN, helpers.psnr(img, ref)
+    # sample-exact except where a path meets a near-tie between coplanar / touching building faces (instances overlap): those
+    # pixel-samples take another but equally valid path -- well under 1 % of the pixels
+    frac = float((np.abs(img - ref).max(-1) > 2e-5 * max(1.0, float(ref.max()))).mean())
+    print("%s: PSNR %.1f dB, %.3f %% of the pixels off by more than fp32 film-sum noise" % (key, helpers.psnr(img, ref), 100 * frac))
+    assert frac <= 1e-2
+
+
+def test_russian_roulette_default_configuration_statistics():
+    """The integrator's DEFAULT configuration (russian_roulette_min_bounces = 0) is the documented non-sample-exact case: the
+    reference draws roulette numbers from a rand()-seeded generator, the device from a per-path hash.  Both are unbiased, so the
+    converged images must agree within noise: committed 1024-spp reference render vs 1024 spp on the GPU."""
+    ref = np.load(os.path.join(GOLD, "pt_rr.npz"))["rr_on"][..., :3].astype(np.float64)
+    yi = _gpu(**RR_ON)
+    img = yi.render()[..., :3].astype(np.float64)
+    off = _gpu(**dict(RR_ON, rr_min_bounces=RR_ON["bounces"])).render()[..., :3].astype(np.float64)     # roulette off: the exact estimator
+    assert abs(img.mean() / ref.mean() - 1.0) < 0.01 and abs(off.mean() / ref.mean() - 1.0) < 0.01
+    h, w = ref.shape[:2]
+    blk = lambda a: a[: h - h % 6, : w - w % 8].reshape(h // 6, 6, w // 8, 8, 3).mean((1, 3))
+    rel = np.abs(blk(img) - blk(ref)) / np.maximum(blk(ref), 0.02)
+    assert np.median(rel) < 0.02 and rel.max() < 0.25, (float(np.median(rel)), float(rel.max()))
+    # roulette really ran: it terminates paths early, so fewer rays are traced than with roulette off
+    assert helpers.psnr(img, ref) > 25.0
