@@ -64,6 +64,7 @@ def parse_args():
     ap.add_argument("--no-raybatch", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--only-raybatch", action="store_true", help="(profiling runs) skip the path tracer part")
     args = ap.parse_args()
     if args.workload == "c4" and args.pt_width == 1920 and args.pt_height == 1080:
         args.pt_width, args.pt_height = 3840, 2160
@@ -307,6 +308,31 @@ def load_peaks():
         return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md; MEASURED_PEAKS.json absent)"
 
 
+def issue_rate(env):
+    """warp-instructions the GPU can issue per second: SMs x 4 schedulers x SM clock (the clock bench.py samples under load)."""
+    torch = env["torch"]
+    sms = torch.cuda.get_device_properties(env["dev"]).multi_processor_count
+    mhz = None
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            mhz = float(json.load(f)["sm_max_mhz"])
+    except Exception:
+        pass
+    mhz = mhz or 1965.0
+    return sms * 4 * mhz * 1e6, "%d SMs x 4 schedulers x %.0f MHz (1 warp-instruction per scheduler and clock)" % (sms, mhz)
+
+
+def load_profile_json(name, want):
+    path = os.path.join(ROOT, "profiles", name)
+    try:
+        t = json.load(open(path))
+        if t.get("workload") != want:
+            return None, "profiles/%s is for '%s', this run is '%s'" % (name, t.get("workload"), want)
+        return t, "profiles/%s (%s)" % (name, t.get("source"))
+    except (OSError, KeyError, ValueError) as e:
+        return None, "no capture: %s" % e
+
+
 def raybatch_arm(args, env):
     """Ray batches (device-resident + end-to-end with host buffers) -> dict on rank 0, None elsewhere.
     workload c2 / c4: C3 (1M-triangle sphere: primary, shadow, diffuse); c5: the 50M-triangle soup (incoherent closest, any-hit segments)."""
@@ -428,6 +454,21 @@ def raybatch_arm(args, env):
         dom = max(BATCHES, key=lambda b: per_ms[b])
         achieved = alg[dom]["bytes_per_ray"] * n / (per_ms[dom] * 1e-3) * 1e-9
         value = float(len(BATCHES)) * n * world * args.steps / (total_ms * 1e-3) * 1e-6
+        want = ("soup %d tris %d rays" % (args.soup_tris, n_total)) if soup else ("sphere nu%d res%d" % (args.nu, args.res))
+        prof, prof_src = load_profile_json("rb_classes_c5.json" if soup else "rb_classes.json", want)
+        irate, irate_src = issue_rate(env)
+        per_batch_roof = {}
+        for b in BATCHES:
+            r_hbm = peak * 1e9 / alg[b]["bytes_per_ray"] * 1e-6                      # Mrays/s if every algorithmic byte came from HBM at the measured peak
+            ent = {"achieved_mrays_s": n / per_ms[b] * 1e-3, "r_hbm_mrays_s": r_hbm}
+            if prof and b in prof["batches"]:
+                pb = prof["batches"][b]
+                wpr = pb["warp_inst"] / n_total                                       # warp-instructions per ray (ncu: smsp__inst_executed.sum)
+                ent.update({"r_issue_mrays_s": irate / wpr * 1e-6, "warp_inst_per_ray": wpr, "active_lanes_per_inst": pb["active_lanes_per_inst"],
+                            "dram_bytes_per_ray_measured": pb["dram_bytes"] / n_total})
+                ent["binding"] = "issue" if ent["r_issue_mrays_s"] < r_hbm else "hbm"
+                ent["frac_of_binding"] = ent["achieved_mrays_s"] / min(ent["r_issue_mrays_s"], r_hbm)
+            per_batch_roof[b] = ent
         line = {
             "metric": RB_METRIC_C5 if soup else RB_METRIC, "value": value, "unit": RB_UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms / args.steps, "scaling": args.scaling, "config": config_dict(args, world),
@@ -437,8 +478,11 @@ def raybatch_arm(args, env):
             "gpu_launches": int(launches),
             "roofline": {
                 "bound": "hbm", "kernel": "k_trace<%s> (%s batch)" % ("SHADOW" if kinds[dom] == acc.isShadowed else "CLOSEST", dom),
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": (prof["batches"][dom]["dram_bytes"] if prof and dom in prof["batches"] else None), "traffic_source": prof_src,
                 "peak_source": peak_src, "launch_ms": per_ms[dom],
+                # north_star: the roofline is the slower of (algorithmic bytes per ray / HBM bandwidth) and the instruction-issue bound
+                "min_of_hbm_and_issue": per_batch_roof, "issue_rate_source": irate_src,
                 "algorithmic_bytes_per_ray": alg[dom]["bytes_per_ray"], "per_batch": alg,
                 "note": "algorithmic bytes = 32 B ray + 16 B hit + 80 B x BVH8 nodes visited + 48 B x triangles tested (SURVEY.md 8(d)); "
                         "most node/triangle fetches are served by L2, DRAM traffic is far lower (see profiles/)",
@@ -565,11 +609,17 @@ SHADE_BYTES = {
 }
 
 
+def pt_workload_key(args):
+    return "%s %dx%d spp%d bounces%d" % ("city%d" % args.city_tris if args.workload == "c4" else "cornell", args.pt_width, args.pt_height, args.pt_spp, args.pt_bounces)
+
+
 def measured_traffic(class_name, args):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel class, from the committed ncu capture of one
     pass of the same workload (tools/ncu_traffic.py -> profiles/pt_traffic.json); None when the workload differs."""
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "pt_traffic.json")
-    want = "cornell %dx%d spp%d bounces%d" % (args.pt_width, args.pt_height, args.pt_spp, args.pt_bounces)
+    want = pt_workload_key(args)
+    if args.workload == "c4":
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "pt_traffic_c4.json")
     try:
         t = json.load(open(path))
         if t.get("workload") != want:
@@ -685,6 +735,32 @@ def pt_arm(args, env):
     }
     achieved = alg_bytes[dom] / (cms[dom] * 1e-3) * 1e-9 if cms[dom] > 0 else 0.0
     traffic, traffic_src = measured_traffic(names[dom], args)
+    # north_star: roofline = the slower of (bytes / HBM bandwidth) and the instruction-issue bound.  Warp-instructions per class
+    # come from the committed ncu launch list of this workload (smsp__inst_executed.sum, tools/ncu_traffic.py -> profiles/pt_traffic.json)
+    irate, irate_src = issue_rate(env)
+    tj, _ = load_profile_json("pt_traffic_c4.json" if args.workload == "c4" else "pt_traffic.json", pt_workload_key(args))
+    per_class, tot_hbm_ms, tot_issue_ms = {}, 0.0, 0.0
+    for k in range(6):
+        if not prof["class_launches"][k]:
+            continue
+        ent = {"ms": cms[k], "hbm_bound_ms": alg_bytes[k] / (peak * 1e9) * 1e3}
+        c = tj["classes"].get(names[k]) if tj else None
+        if c and c.get("warp_inst"):
+            winst = c["warp_inst_per_launch"] * prof["class_launches"][k]
+            ent.update({"issue_bound_ms": winst / irate * 1e3, "warp_inst_per_pass": winst, "active_lanes_per_inst": c.get("active_lanes_per_inst"),
+                        "dram_bytes_per_pass_measured": c["dram_bytes_per_launch"] * prof["class_launches"][k]})
+            ent["binding"] = "issue" if ent["issue_bound_ms"] > ent["hbm_bound_ms"] else "hbm"
+            ent["frac_of_binding"] = max(ent["issue_bound_ms"], ent["hbm_bound_ms"]) / cms[k] if cms[k] > 0 else None
+            tot_issue_ms += ent["issue_bound_ms"]
+        tot_hbm_ms += ent["hbm_bound_ms"]
+        per_class[names[k]] = ent
+    pass_ms = total_ms / args.steps
+    pass_roof = {"hbm_bound_ms": tot_hbm_ms, "issue_bound_ms": tot_issue_ms or None, "pass_ms_timed": pass_ms,
+                 "r_hbm_msamples_s": n / tot_hbm_ms * 1e-3, "r_issue_msamples_s": (n / tot_issue_ms * 1e-3) if tot_issue_ms else None,
+                 "achieved_msamples_s": n / pass_ms * 1e-3}
+    if tot_issue_ms:
+        pass_roof["binding"] = "issue" if tot_issue_ms > tot_hbm_ms else "hbm"
+        pass_roof["frac_of_binding"] = max(tot_issue_ms, tot_hbm_ms) / pass_ms
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
@@ -700,6 +776,9 @@ def pt_arm(args, env):
             "launch_ms": cms[dom] / max(1, prof["class_launches"][dom]),
             "class_ms_per_pass": dict(zip(names, cms)), "class_launches_per_pass": dict(zip(names, prof["class_launches"][:6])),
             "class_algorithmic_GB": {names[k]: alg_bytes[k] * 1e-9 for k in range(6)},
+            "min_of_hbm_and_issue": {"per_class": per_class, "whole_pass": pass_roof, "issue_rate_source": irate_src,
+                                     "note": "hbm_bound_ms = algorithmic bytes / measured HBM peak; issue_bound_ms = warp-instructions (ncu) / issue rate; "
+                                             "binding = the slower bound; frac_of_binding = bound / measured time (whole pass: against the timed, lane-overlapped pass)"},
             "pass_ms_profiled": sum(cms),
             "pass_ms_timed": total_ms / args.steps,
             "note": "class times come from one profiled pass whose kernels run one by one on one stream; the timed passes overlap "
@@ -753,7 +832,7 @@ def main():
 
     env = {"torch": torch, "dist": dist, "world": world, "rank": rank, "local": local, "dev": dev, "barrier": barrier,
            "sampler": ClockSampler(local) if rank == 0 else None}
-    if args.workload == "c5":
+    if args.workload == "c5" or args.only_raybatch:
         # the soup has no path-traced part: its ray batches are the line
         line = raybatch_arm(args, env)
         if rank == 0:

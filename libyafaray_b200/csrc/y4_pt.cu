@@ -40,10 +40,14 @@ struct Y4Pt
 		Y4PtWave wave = {};
 		void *mem = nullptr;
 		uint32_t *q_hit0 = nullptr, *q_path[2] = {nullptr, nullptr}, *q_shadow = nullptr, *q_spec[2] = {nullptr, nullptr};   // index queues (in mem)
+		// Compacting bounce loop: the paths of the bounce loop live in two dense "path waves" and move from one to the other at
+		// every bounce, live paths packed at the front (k_pt_path_compact); corig = the pixel-sample slot a path belongs to
+		Y4PtWave cw[2] = {{}, {}}; uint32_t *corig[2] = {nullptr, nullptr}; void *cmem = nullptr; uint32_t ccap = 0;
 		cudaStream_t stream = nullptr;      // lane 0: the context's stream; lane 1: own stream, forked/joined per pass
 		cudaEvent_t done = nullptr;
 	} lanes[kMaxLanes];
 	int n_lanes = 2, trace_blocks_shared = 2;
+	int compact = 1;             // env Y4GPU_PT_COMPACT=0: the bounce loop over index queues into the pixel-sample wave (no path movement)
 	cudaEvent_t ev_fork = nullptr;
 	// per-launch counters: 64-bit slots, zeroed once per pass; a queue length is the low word of its slot
 	unsigned long long *d_counters = nullptr, *h_counters = nullptr; size_t counters_cap = 0;
@@ -106,7 +110,7 @@ template<int STAGE, int MINB, bool SPEC>
 __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, StageArgs a, StageQueues Q)
 {
 	const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
-	const uint32_t count = Q.in_q ? *Q.in_count : W.n;
+	const uint32_t count = Q.in_count ? *Q.in_count : W.n;        // in_count without in_q: the first *in_count slots (a dense path wave)
 	const uint32_t stride = gridDim.x * blockDim.x;
 	for(uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < count; base += stride)
 	{
@@ -164,6 +168,119 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 	}
 }
 
+// ---- the per-bounce path stage with compaction ---------------------------------------------------------------
+// Late bounces of a wavefront keep a shrinking, scattered subset of the pixel-samples alive.  Run over index queues into the
+// pixel-sample wave (k_pt_stage<kStPath>) every 16-byte field of such a path costs a whole 32-byte sector, every 4-byte field
+// eight times its size, and partial-sector writes are read-modify-write in L2: ncu measured 650 MB of DRAM traffic per launch
+// from bounce 2 to bounce 7 while the algorithmic bytes fell to 150 MB.  Here the paths of the bounce loop live in their own
+// dense "path waves": a stage reads wave Wr (entry q = slot q, fully coalesced), runs the unchanged per-path logic
+// (y4_stage_path) on a copy of the path's state staged in SHARED memory -- the stage's wave argument simply points there --
+// and writes the paths that go on to the FRONT of wave Ww at the position their queue append reserved.  A path that ends
+// hands its path_col to the pixel-sample it belongs to (W0.pcol[orig]): the only scattered access left.  Traversal then
+// runs over dense rays as well.  The arithmetic per path is exactly that of the queue version.
+constexpr int kCompactThreads = 128;
+constexpr size_t kCompactSmem = (size_t) kCompactThreads * 17 * sizeof(float4);      // 272 B of staged state per thread
+
+template<int MINB, bool SPEC>
+__global__ void __launch_bounds__(kCompactThreads, MINB) k_pt_path_compact(const __grid_constant__ Y4PtScene sc, Y4PtWave Wr, Y4PtWave Ww, Y4PtWave W0, Y4PtPass ps,
+                                                                           StageArgs a, StageQueues Q, const uint32_t *__restrict__ orig_r, uint32_t *__restrict__ orig_w)
+{
+	extern __shared__ float4 y4_stage_smem[];
+	constexpr uint32_t T = kCompactThreads;
+	Y4PtWave S = {};
+	{
+		float4 *p = y4_stage_smem;
+		S.n = T;
+		S.lsamp = (float *) p; p += T; S.thr = (float *) p; p += T; S.pthr = (float *) p; p += T; S.pcol = (float *) p; p += T;
+		S.lcol = (float *) p; p += T;          // (acc_a / acc_b: only lights with several samples use them, and those scenes take the queue version)
+		S.ray = (Y4Ray *) p; S.ray_next = S.ray; p += 2 * T;        // the stage reads its ray before it writes the next one: one slot
+		S.hit = (Y4Hit *) p; p += T;
+		S.sray = (Y4Ray *) p; p += 4 * T; S.shit = (Y4Hit *) p; p += 2 * T; S.scontrib = (float *) p; p += 2 * T;
+		S.flags = (uint32_t *) p; S.pix = S.flags + T; S.samp = S.pix + T; S.lnum = S.samp + T;
+	}
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, lt_mask = (1u << lane) - 1u;
+	const uint32_t count = *Q.in_count;
+	const uint32_t stride = gridDim.x * T;
+	const bool closing = a.depth >= sc.bounces;
+	for(uint32_t base = blockIdx.x * T + (tid & ~31u); base < count; base += stride)
+	{
+		const uint32_t q = base + lane;
+		const bool have = q < count;
+		uint32_t push = 0u, orig = 0u;
+		if(have)
+		{
+			const uint32_t j = Q.in_q ? Q.in_q[q] : q;
+			orig = orig_r ? orig_r[j] : j;
+			const uint32_t f = Wr.flags[j];
+			// copy-in: everything y4_stage_path can read, requested together (dense: one coalesced access per field and warp)
+			const float4 v_pcol = ld4(Wr.pcol, j), v_pthr = ld4(Wr.pthr, j), v_sc0 = ld4(Wr.scontrib, j);
+			float4 v_lsamp = v_pcol, v_thr = v_pcol, v_hit = v_pcol, v_r0 = v_pcol, v_r1 = v_pcol;
+			uint32_t pix = 0u, samp = 0u;
+			if(!closing)
+			{
+				v_lsamp = ld4(Wr.lsamp, j); v_thr = ld4(Wr.thr, j); v_hit = *reinterpret_cast<const float4 *>(Wr.hit + j);
+				v_r0 = reinterpret_cast<const float4 *>(Wr.ray + j)[0]; v_r1 = reinterpret_cast<const float4 *>(Wr.ray + j)[1];
+				pix = Wr.pix[j]; samp = Wr.samp[j];
+			}
+			if(f & Y4_PF_C1) st4(S.scontrib, T + tid, ld4(Wr.scontrib, Wr.n + j));
+			if(f & Y4_PF_S0) *reinterpret_cast<float4 *>(S.shit + tid) = *reinterpret_cast<const float4 *>(Wr.shit + j);
+			if(f & Y4_PF_S1) *reinterpret_cast<float4 *>(S.shit + T + tid) = *reinterpret_cast<const float4 *>(Wr.shit + Wr.n + j);
+			if(f & Y4_PF_LCOL) st4(S.lcol, tid, ld4(Wr.lcol, j));
+			if(sc.n_lights > 1) S.lnum[tid] = Wr.lnum[j];
+			S.flags[tid] = f; S.pix[tid] = pix; S.samp[tid] = samp;
+			st4(S.pcol, tid, v_pcol); st4(S.pthr, tid, v_pthr); st4(S.scontrib, tid, v_sc0);
+			if(!closing)
+			{
+				st4(S.lsamp, tid, v_lsamp); st4(S.thr, tid, v_thr); *reinterpret_cast<float4 *>(S.hit + tid) = v_hit;
+				reinterpret_cast<float4 *>(S.ray + tid)[0] = v_r0; reinterpret_cast<float4 *>(S.ray + tid)[1] = v_r1;
+			}
+			push = y4_stage_path<SPEC>(sc, S, ps, tid, a.depth, a.sub, a.k_prev);
+		}
+		// queue appends: one 64-bit atomic per warp reserves the path range (low word) and the shadow-ray range (high word)
+		const uint32_t m0 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S0), m1 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S1);
+		const uint32_t mp = __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH);
+		uint32_t at_sh = 0u, at_p = 0u;
+		if(m0 | m1 | mp)
+		{
+			if(lane == 0)
+			{
+				const uint32_t n_sh = (uint32_t) (__popc(m0) + __popc(m1)), n_p = (uint32_t) __popc(mp);
+				const unsigned long long old = atomicAdd(reinterpret_cast<unsigned long long *>(Q.out_count), ((unsigned long long) n_sh << 32) | n_p);
+				at_p = (uint32_t) old; at_sh = (uint32_t) (old >> 32);
+			}
+			at_sh = __shfl_sync(0xffffffffu, at_sh, 0);
+			at_p = __shfl_sync(0xffffffffu, at_p, 0);
+		}
+		if(push & Y4_PUSH_PATH)
+		{
+			// copy-out to the front of the other path wave
+			const uint32_t o = at_p + __popc(mp & lt_mask);
+			const uint32_t f = S.flags[tid];
+			Ww.flags[o] = f; Ww.pix[o] = S.pix[tid]; Ww.samp[o] = S.samp[tid]; orig_w[o] = orig;
+			if(sc.n_lights > 1) Ww.lnum[o] = S.lnum[tid];
+			st4(Ww.lsamp, o, ld4(S.lsamp, tid)); st4(Ww.thr, o, ld4(S.thr, tid)); st4(Ww.pthr, o, ld4(S.pthr, tid)); st4(Ww.pcol, o, ld4(S.pcol, tid));
+			if(f & Y4_PF_LCOL) st4(Ww.lcol, o, ld4(S.lcol, tid));
+			reinterpret_cast<float4 *>(Ww.ray + o)[0] = reinterpret_cast<const float4 *>(S.ray + tid)[0];
+			reinterpret_cast<float4 *>(Ww.ray + o)[1] = reinterpret_cast<const float4 *>(S.ray + tid)[1];
+			if(f & Y4_PF_DIRECT) st4(Ww.scontrib, o, ld4(S.scontrib, tid));
+			if(f & Y4_PF_C1) st4(Ww.scontrib, Ww.n + o, ld4(S.scontrib, T + tid));
+			if(push & Y4_PUSH_S0)
+			{
+				reinterpret_cast<float4 *>(Ww.sray + o)[0] = reinterpret_cast<const float4 *>(S.sray + tid)[0];
+				reinterpret_cast<float4 *>(Ww.sray + o)[1] = reinterpret_cast<const float4 *>(S.sray + tid)[1];
+				Q.sh_q[at_sh + __popc(m0 & lt_mask)] = o;
+			}
+			if(push & Y4_PUSH_S1)
+			{
+				reinterpret_cast<float4 *>(Ww.sray + Ww.n + o)[0] = reinterpret_cast<const float4 *>(S.sray + T + tid)[0];
+				reinterpret_cast<float4 *>(Ww.sray + Ww.n + o)[1] = reinterpret_cast<const float4 *>(S.sray + T + tid)[1];
+				Q.sh_q[at_sh + __popc(m0) + __popc(m1 & lt_mask)] = Ww.n + o;
+			}
+		}
+		else if(have) st4(W0.pcol, orig, ld4(S.pcol, tid));        // the path ended: its path_col goes home to the pixel-sample
+	}
+}
+
 __global__ void __launch_bounds__(kPtThreads) k_pt_tri_shade(const float *__restrict__ verts, const uint32_t *__restrict__ tri_flags, uint32_t n_mats, uint64_t n_tri, float4 *__restrict__ out)
 {
 	for(uint64_t t = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x; t < n_tri; t += (uint64_t) gridDim.x * blockDim.x) out[t] = y4_tri_shade(verts, tri_flags, n_mats, t);
@@ -217,6 +334,32 @@ inline int pt_grid(const y4gpu_ctx *ctx, uint32_t n)
 void pt_free_wave(Y4Pt::Lane &L)
 {
 	cudaFree(L.mem); L.mem = nullptr; L.cap = 0;
+	cudaFree(L.cmem); L.cmem = nullptr; L.ccap = 0;
+}
+
+// The two dense path waves of the compacting bounce loop: only the fields the bounce loop moves (308 B per slot and wave).
+int pt_alloc_compact(y4gpu_ctx *ctx, Y4Pt::Lane &L, uint32_t cap)
+{
+	if(cap <= L.ccap) return Y4GPU_OK;
+	cudaFree(L.cmem); L.cmem = nullptr; L.ccap = 0;
+	const size_t n = cap;
+	const size_t per_wave = n * (5 * 4 /*flags pix samp lnum orig*/ + 7 * 16 /*lsamp thr pthr pcol lcol acc_a acc_b*/ + 32 + 16 /*ray hit*/ + 2 * 32 + 2 * 16 + 2 * 16 /*shadow*/) + 512;
+	Y4_CUDA(ctx, cudaMalloc(&L.cmem, 2 * per_wave));
+	char *p = (char *) L.cmem;
+	auto take = [&](size_t b) { char *r = p; p += (b + 15) & ~(size_t) 15; return (void *) r; };
+	for(int k = 0; k < 2; ++k)
+	{
+		Y4PtWave &W = L.cw[k];
+		W = Y4PtWave{};
+		W.lsamp = (float *) take(n * 16); W.thr = (float *) take(n * 16); W.pthr = (float *) take(n * 16); W.pcol = (float *) take(n * 16);
+		W.lcol = (float *) take(n * 16); W.acc_a = (float *) take(n * 16); W.acc_b = (float *) take(n * 16);
+		W.ray = (Y4Ray *) take(n * 32); W.ray_next = W.ray; W.hit = (Y4Hit *) take(n * 16);
+		W.sray = (Y4Ray *) take(2 * n * 32); W.shit = (Y4Hit *) take(2 * n * 16); W.scontrib = (float *) take(2 * n * 16);
+		W.flags = (uint32_t *) take(n * 4); W.pix = (uint32_t *) take(n * 4); W.samp = (uint32_t *) take(n * 4); W.lnum = (uint32_t *) take(n * 4);
+		L.corig[k] = (uint32_t *) take(n * 4);
+	}
+	L.ccap = cap;
+	return Y4GPU_OK;
 }
 
 // One allocation carved into the SoA arrays of the wave (all 16-byte aligned).
@@ -374,6 +517,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	if(const char *e = getenv("Y4GPU_PT_MIN_BLOCKS")) ctx->pt->stage_min_blocks = atoi(e);
 	if(const char *e = getenv("Y4GPU_PT_LANES")) ctx->pt->n_lanes = atoi(e) < 1 ? 1 : (atoi(e) > kMaxLanes ? kMaxLanes : atoi(e));
 	if(const char *e = getenv("Y4GPU_PT_TRACE_BLOCKS")) ctx->pt->trace_blocks_shared = atoi(e);
+	if(const char *e = getenv("Y4GPU_PT_COMPACT")) ctx->pt->compact = atoi(e);
 	Y4Pt *pt = ctx->pt;
 	if(!pt->ev0) { Y4_CUDA(ctx, cudaEventCreate(&pt->ev0)); Y4_CUDA(ctx, cudaEventCreate(&pt->ev1)); }
 	cudaStream_t st = ctx->stream;
@@ -716,6 +860,21 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		if(!pt->lanes[l].done) Y4_CUDA(ctx, cudaEventCreateWithFlags(&pt->lanes[l].done, cudaEventDisableTiming));
 	}
 	for(int l = 0; l < n_lanes; ++l) { const int rc = pt_alloc_wave(ctx, pt->lanes[l], wave_size); if(rc) return rc; }
+	// the compacting bounce loop carries no incoming ray / hit for extra light samples at a path vertex (k > 0): lights with one sample only
+	const bool compact = pt->compact != 0 && pt->max_light_samples == 1 && sc.n_paths > 0;
+	if(compact)
+	{
+		for(int l = 0; l < n_lanes; ++l) { const int rc = pt_alloc_compact(ctx, pt->lanes[l], wave_size); if(rc) return rc; }
+		static bool smem_set[16] = {false};
+		if(!smem_set[ctx->device & 15])
+		{
+			Y4_CUDA(ctx, cudaFuncSetAttribute(k_pt_path_compact<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kCompactSmem));
+			Y4_CUDA(ctx, cudaFuncSetAttribute(k_pt_path_compact<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kCompactSmem));
+			Y4_CUDA(ctx, cudaFuncSetAttribute(k_pt_path_compact<5, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kCompactSmem));
+			Y4_CUDA(ctx, cudaFuncSetAttribute(k_pt_path_compact<6, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kCompactSmem));
+			smem_set[ctx->device & 15] = true;
+		}
+	}
 	const int trace_blocks = n_lanes > 1 ? pt->trace_blocks_shared : 0;
 	const int shadow_kind = pt->params.transp_shadows ? Y4_TRACE_TSHADOW : Y4_TRACE_SHADOW;
 	const int stage_minb = n_lanes > 1 && pt->stage_min_blocks < 3 ? 3 : pt->stage_min_blocks;
@@ -851,6 +1010,41 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 			Q.in_q = lane.q_hit0; Q.in_count = n_hit0; Q.out_q = lane.q_path[cur]; Q.out_count = n_cur; Q.sh_q = lane.q_shadow; Q.sh_count = nullptr;
 			a.all_lights = 1; a.sub = sub; a.l_prev = (sub == 0 && !all_lk.empty()) ? all_lk.back().first : -1; a.k_prev = a.l_prev >= 0 ? all_lk.back().second : -1;
 			Y4_PT_LAUNCH(3, launch_stage<kStStart>(stage_minb, grid, st, dsc, W, ps, a, Q));
+			if(compact)
+			{
+				// bounce 0 reads the pixel-sample wave through the start stage's queue; from then on the paths live in the two dense
+				// path waves, `rd` the one the traced rays / hits are in
+				int rd = -1;
+				for(int depth = 0; depth <= sc.bounces; ++depth)
+				{
+					const bool closing = depth == sc.bounces;
+					if(closing && !sc.n_lights) break;
+					const int wr = rd < 0 ? 0 : (rd ^ 1);
+					Y4PtWave Wr = rd < 0 ? W : lane.cw[rd], Ww = lane.cw[wr];
+					Wr.n = W.n; Ww.n = W.n;
+					if(rd < 0) Wr.ray = ray_buf[0];
+					const uint32_t *in_q = rd < 0 ? lane.q_path[0] : nullptr;
+					if(!closing) Y4_PT_TRACE(Y4_TRACE_CLOSEST, Wr.ray, Wr.hit, W.n, in_q, n_cur);
+					uint32_t *n_next = nullptr;
+					new_queue_pair(depth + 1 < sc.bounces ? 0 : (closing ? -1 : 3), sc.n_lights && !closing ? 1 : -1, n_next, Q.sh_count);
+					Q.in_q = in_q; Q.in_count = n_cur; Q.out_q = nullptr; Q.out_count = n_next; Q.sh_q = lane.q_shadow;
+					a.all_lights = 0; a.depth = depth; a.sub = sub; a.l_prev = -1; a.k_prev = sc.n_lights ? 0 : -1;
+					{
+						const uint32_t want = (W.n + kCompactThreads - 1) / kCompactThreads, full = (uint32_t) ctx->sm_count * 12u;
+						const int cgrid = (int) (want < full ? (want ? want : 1u) : full);
+						const uint32_t *orig_r = rd < 0 ? nullptr : lane.corig[rd];
+						static const int cminb = getenv("Y4GPU_PT_COMPACT_MINB") ? atoi(getenv("Y4GPU_PT_COMPACT_MINB")) : 5;      // 96 registers, 5 CTAs of 128 threads per SM: the measured optimum (profiles/r2_v5_sweep_compact.log)
+						if(sc.has_specular) Y4_PT_LAUNCH(3, (k_pt_path_compact<4, true><<<cgrid, kCompactThreads, kCompactSmem, st>>>(dsc, Wr, Ww, W, ps, a, Q, orig_r, lane.corig[wr])));
+						else if(cminb >= 6) Y4_PT_LAUNCH(3, (k_pt_path_compact<6, false><<<cgrid, kCompactThreads, kCompactSmem, st>>>(dsc, Wr, Ww, W, ps, a, Q, orig_r, lane.corig[wr])));
+						else if(cminb == 5) Y4_PT_LAUNCH(3, (k_pt_path_compact<5, false><<<cgrid, kCompactThreads, kCompactSmem, st>>>(dsc, Wr, Ww, W, ps, a, Q, orig_r, lane.corig[wr])));
+						else Y4_PT_LAUNCH(3, (k_pt_path_compact<4, false><<<cgrid, kCompactThreads, kCompactSmem, st>>>(dsc, Wr, Ww, W, ps, a, Q, orig_r, lane.corig[wr])));
+					}
+					if(closing) break;
+					if(sc.n_lights) Y4_PT_TRACE(shadow_kind, Ww.sray, Ww.shit, 2ull * W.n, lane.q_shadow, Q.sh_count);
+					rd = wr; n_cur = n_next;
+				}
+				continue;
+			}
 			for(int depth = 0; depth <= sc.bounces; ++depth)
 			{
 				const bool closing = depth == sc.bounces;

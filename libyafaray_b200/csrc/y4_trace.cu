@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 			const uint64_t mine = base + __popc(idle & lt_mask);
 			if(!have && mine < n)
 			{
-				const uint64_t slot_i = QUEUE ? (uint64_t) __ldg(queue + mine) : mine;
+				const uint64_t slot_i = (QUEUE && queue) ? (uint64_t) __ldg(queue + mine) : mine;      // QUEUE without a queue: the first *queue_count slots
 				const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + slot_i));
 				const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + slot_i) + 1);
 				Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
@@ -298,10 +298,11 @@ int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_
 	TraceArgs a; a.rays = d_rays; a.n = n_max; a.out = d_out; a.work_counter = d_work_counter; a.visit = d_visit; a.queue = d_queue; a.queue_count = d_queue_count;
 	a.stream = stream; a.max_blocks_per_sm = max_blocks_per_sm;
 	int rc;
-	if(kind == Y4_TRACE_CLOSEST) rc = d_queue ? launch<Y4_TRACE_CLOSEST, true>(ctx, counted, a) : launch<Y4_TRACE_CLOSEST, false>(ctx, counted, a);
-	else if(kind == Y4_TRACE_SHADOW) rc = d_queue ? launch<Y4_TRACE_SHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_SHADOW, false>(ctx, counted, a);
+	const bool queued = d_queue || d_queue_count;       // a count without a queue: the dense front of a path wave
+	if(kind == Y4_TRACE_CLOSEST) rc = queued ? launch<Y4_TRACE_CLOSEST, true>(ctx, counted, a) : launch<Y4_TRACE_CLOSEST, false>(ctx, counted, a);
+	else if(kind == Y4_TRACE_SHADOW) rc = queued ? launch<Y4_TRACE_SHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_SHADOW, false>(ctx, counted, a);
 	// opaque-only transparent-shadow query of the path tracer: intersectTs ray range and visibility, first blocker ends the ray
-	else if(kind == Y4_TRACE_TSHADOW) rc = d_queue ? launch<Y4_TRACE_TSHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_TSHADOW, false>(ctx, counted, a);
+	else if(kind == Y4_TRACE_TSHADOW) rc = queued ? launch<Y4_TRACE_TSHADOW, true>(ctx, counted, a) : launch<Y4_TRACE_TSHADOW, false>(ctx, counted, a);
 	else { ctx->err = "bad trace kind"; return Y4GPU_ERR_ARG; }
 	if(rc) return rc;
 	ctx->stats.kernel_launches++;

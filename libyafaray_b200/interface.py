@@ -662,11 +662,21 @@ class Interface:
 
             npx = a["params"].width * a["params"].height
             dev = torch.device("cuda", self.device)
+            # kernels, the collective and the film adds are ordered by ONE stream.  It cannot be torch's default stream: its
+            # handle is 0, which y4gpu_set_stream reads as "use the context's own stream", and that non-blocking stream is not
+            # ordered against the legacy default stream
+            cur = torch.cuda.current_stream(dev)
+            if cur.cuda_stream == 0:
+                if getattr(self, "_torch_stream", None) is None:
+                    self._torch_stream = torch.cuda.Stream(device=dev)
+                cur = self._torch_stream
+            self._shard_stream = cur
             if self._pass_film is None or self._pass_film.numel() != 5 * npx:
-                self._pass_film = torch.zeros(5 * npx, device=dev, dtype=torch.float32)
-                self._total_film = torch.zeros(5 * npx, device=dev, dtype=torch.float32)
+                with torch.cuda.stream(cur):
+                    self._pass_film = torch.zeros(5 * npx, device=dev, dtype=torch.float32)
+                    self._total_film = torch.zeros(5 * npx, device=dev, dtype=torch.float32)
             self.film_buffers = (self._pass_film[:npx], self._pass_film[npx:])
-            self.accelerator.set_stream(torch.cuda.current_stream(dev).cuda_stream)     # kernels, collective and adds on one stream
+            self.accelerator.set_stream(cur.cuda_stream)
         if self.film_buffers is not None:
             w, rgba = self.film_buffers
             _lib.check(ctx, L.y4gpu_pt_set_film_buffers(ctx, C.c_void_p(w.data_ptr()), C.c_void_p(rgba.data_ptr())), "y4gpu_pt_set_film_buffers")
@@ -682,9 +692,12 @@ class Interface:
         to the total film.  Queued on the stream the pass ran on; nothing is synchronised."""
         if not self.sharded:
             return
-        self.comm.all_reduce(self._pass_film)
-        self._total_film.add_(self._pass_film)
-        self._pass_film.zero_()
+        import torch
+
+        with torch.cuda.stream(self._shard_stream):
+            self.comm.all_reduce(self._pass_film)
+            self._total_film.add_(self._pass_film)
+            self._pass_film.zero_()
 
     def render_pass_reduced(self, n_samples: int, offset: int, aa_pass: int, pixel_list=None):
         """render_pass on this rank's shard of the samples + reduce_pass: afterwards every rank holds the complete film."""
@@ -755,7 +768,10 @@ class Interface:
         if self.sharded:
             if mode != "none":
                 raise Y4Error("film_load_save_mode together with multi-GPU sharding is not supported (save the film from rank 0's read_film())")
-            self._total_film.zero_()
+            import torch
+
+            with torch.cuda.stream(self._shard_stream):
+                self._total_film.zero_()
         stats = {"samples": 0, "rays_closest": 0, "rays_shadow": 0, "kernel_launches": 0, "pass_ms": 0.0}
         self.resumed = resumed is not None
         if resumed is not None:                                 # renderPass(0, film sampling offset): nothing is rendered
@@ -832,8 +848,10 @@ class Interface:
             import torch
 
             npx = pr.height * pr.width
-            torch.from_numpy(w.reshape(-1)).copy_(self._total_film[:npx])
-            torch.from_numpy(rgba.reshape(-1)).copy_(self._total_film[npx:])
+            with torch.cuda.stream(self._shard_stream):
+                torch.from_numpy(w.reshape(-1)).copy_(self._total_film[:npx])
+                torch.from_numpy(rgba.reshape(-1)).copy_(self._total_film[npx:])
+            self._shard_stream.synchronize()
             return w, rgba
         _lib.check(ctx, L.y4gpu_pt_read_film(ctx, C.c_void_p(w.ctypes.data), C.c_void_p(rgba.ctypes.data)), "y4gpu_pt_read_film")
         return w, rgba
