@@ -65,6 +65,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--only-raybatch", action="store_true", help="(profiling runs) skip the path tracer part")
+    ap.add_argument("--no-profile", action="store_true", help="(ncu runs) skip the extra profiled pass; the line then carries no roofline")
     args = ap.parse_args()
     if args.workload == "c4" and args.pt_width == 1920 and args.pt_height == 1080:
         args.pt_width, args.pt_height = 3840, 2160
@@ -705,6 +706,12 @@ def pt_arm(args, env):
         ye.clearAll()
 
     # ---- one profiled pass: device time per kernel class + BVH visit counters (for the roofline) ----
+    if args.no_profile:
+        if rank == 0:
+            print_json({"metric": METRIC, "value": W * H * spp_step * args.steps / (total_ms * 1e-3) * 1e-6, "unit": UNIT, "ms_per_step": total_ms / args.steps,
+                        "note": "--no-profile run (for ncu): no roofline"})
+        yi.clearAll()
+        raise SystemExit(0)
     yp = make(profile=1)
     yp.upload()
     yp.render_pass(spp_step, 0, 0)

@@ -197,6 +197,20 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 			m.mirror_color[0] = m.mirror_color[1] = m.mirror_color[2] = 1.f; m.ior = 1.33f; m.transmit_filter = 1.f; m.diffuse_reflect = 1.f;
 			if(type == "light_mat") { m.type = Y4GPU_MAT_LIGHT; m.emit = get<float>(p, "power", 1.f); m.double_sided = get<bool>(p, "double_sided", false); }
 			else if(type == "mirror") { m.type = Y4GPU_MAT_MIRROR; m.diffuse_reflect = get<float>(p, "reflect", 1.f); }
+			else if(type == "glass")
+			{
+				// GlassMaterial::factory (material_glass.cc:290-433): IOR / transmit_filter / dispersion_power are double parameters
+				if(get<double>(p, "dispersion_power", 0.0) > 0.0 || get<bool>(p, "fake_shadows", false)) unsupported("glass '" + mat_names[i] + "': dispersion / fake_shadows");
+				const Rgb ab = getCol(p, "absorption", Rgb{1.f});
+				if(ab.r_ < 1.f || ab.g_ < 1.f || ab.b_ < 1.f) unsupported("glass '" + mat_names[i] + "': absorption");
+				if(get<float>(p, "wireframe_amount", 0.f) != 0.f || get<float>(p, "samplingfactor", 1.f) != 1.f || get<int>(p, "additionaldepth", 0) != 0) unsupported("glass '" + mat_names[i] + "': wireframe / samplingfactor / additionaldepth");
+				for(const auto &kv : p) if(kv.first.size() > 7 && kv.first.compare(kv.first.size() - 7, 7, "_shader") == 0) unsupported("glass '" + mat_names[i] + "': shader nodes");
+				m.type = Y4GPU_MAT_GLASS;
+				m.ior = (float) get<double>(p, "IOR", 1.4);
+				const double filt = get<double>(p, "transmit_filter", 0.0);
+				put3(m.color, filt * getCol(p, "filter_color", Rgb{1.f}) + Rgb(1.f - filt));      // the constructor argument, formed like the factory does
+				put3(m.mirror_color, getCol(p, "mirror_color", Rgb{1.f}));
+			}
 			else if(type == "shinydiffusemat")
 			{
 				m.type = Y4GPU_MAT_SHINYDIFFUSE;

@@ -102,7 +102,7 @@ class PtAaNoise(C.Structure):
                 ("variance_edge_size", C.c_int32), ("variance_pixels", C.c_int32), ("reserved", C.c_int32 * 6)]  # fmt: skip
 
 
-MAT_SHINYDIFFUSE, MAT_LIGHT, MAT_MIRROR = 0, 1, 2
+MAT_SHINYDIFFUSE, MAT_LIGHT, MAT_MIRROR, MAT_GLASS = 0, 1, 2, 3
 LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT, LIGHT_OBJECT = 0, 1, 2, 3, 4, 5, 6
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
 CAMERA_TYPES = {"perspective": 0, "architect": 1, "orthographic": 2, "equirectangular": 3}

@@ -43,6 +43,8 @@ struct Y4Pt
 		// Compacting bounce loop: the paths of the bounce loop live in two dense "path waves" and move from one to the other at
 		// every bounce, live paths packed at the front (k_pt_path_compact); corig = the pixel-sample slot a path belongs to
 		Y4PtWave cw[2] = {{}, {}}; uint32_t *corig[2] = {nullptr, nullptr}; void *cmem = nullptr; uint32_t ccap = 0;
+		// ray-tree mode: per pixel-sample stack of pending sibling branches (ray 32 B + weight 16 B per entry) + its height
+		void *tmem = nullptr; uint32_t tcap = 0; int tdepth = 0;
 		cudaStream_t stream = nullptr;      // lane 0: the context's stream; lane 1: own stream, forked/joined per pass
 		cudaEvent_t done = nullptr;
 	} lanes[kMaxLanes];
@@ -83,7 +85,7 @@ namespace {
 
 constexpr int kPtThreads = 256;
 
-enum { kStPrimary, kStDirectStep, kStStart, kStPath, kStLevelFinish };
+enum { kStPrimary, kStDirectStep, kStStart, kStPath, kStLevelFinish, kStPrimary3, kStFinish3 };      // ...3: ray-tree mode (has_specular == 3)
 struct StageArgs { int all_lights, l_prev, k_prev, l, k, depth, sub, level; };
 struct StageQueues
 {
@@ -123,11 +125,13 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 			else if(STAGE == kStDirectStep) push = y4_stage_direct_step<SPEC>(sc, W, ps, i, a.all_lights != 0, a.l_prev, a.k_prev, a.l, a.k);
 			else if(STAGE == kStStart) push = y4_stage_start<SPEC>(sc, W, ps, i, a.l_prev, a.k_prev, a.sub);
 			else if(STAGE == kStLevelFinish) push = y4_stage_level_finish(sc, W, ps, i, a.level);
+			else if(STAGE == kStPrimary3) push = y4_stage_primary3(sc, W, ps, i, a.l, a.level);
+			else if(STAGE == kStFinish3) push = y4_stage_finish3(sc, W, ps, i);
 			else push = y4_stage_path<SPEC>(sc, W, ps, i, a.depth, a.sub, a.k_prev);
 		}
 		// queue appends: one atomic per warp; when a stage feeds both queues their two 32-bit lengths share one 64-bit
 		// counter slot (path count low, shadow count high) and a single 64-bit atomic reserves both ranges
-		if(STAGE == kStLevelFinish) push &= Y4_PUSH_SPEC;
+		if(STAGE == kStLevelFinish || STAGE == kStFinish3) push &= Y4_PUSH_SPEC;
 		const uint32_t m0 = (STAGE != kStStart) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_S0) : 0u;
 		const uint32_t m1 = (STAGE != kStStart) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_S1) : 0u;
 		const uint32_t mp = (STAGE != kStDirectStep) ? __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH) : 0u;
@@ -137,7 +141,7 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 			uint32_t at_sh = 0u, at_p = 0u;
 			if(lane == 0)
 			{
-				if((STAGE == kStPrimary || STAGE == kStPath) && Q.sh_count == Q.out_count + 1)
+				if((STAGE == kStPrimary || STAGE == kStPath || STAGE == kStPrimary3) && Q.sh_count == Q.out_count + 1)
 				{
 					const unsigned long long old = atomicAdd(reinterpret_cast<unsigned long long *>(Q.out_count), ((unsigned long long) n_sh << 32) | n_p);
 					at_p = (uint32_t) old; at_sh = (uint32_t) (old >> 32);
@@ -154,7 +158,7 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 			if(push & Y4_PUSH_S1) Q.sh_q[at_sh + __popc(m0) + __popc(m1 & lt_mask)] = W.n + i;
 			if(push & Y4_PUSH_PATH) Q.out_q[at_p + __popc(mp & lt_mask)] = i;
 		}
-		if((STAGE == kStPrimary || STAGE == kStLevelFinish) && Q.spec_q)
+		if((STAGE == kStPrimary || STAGE == kStLevelFinish || STAGE == kStPrimary3 || STAGE == kStFinish3) && Q.spec_q)
 		{
 			const uint32_t ms = __ballot_sync(0xffffffffu, push & Y4_PUSH_SPEC);
 			if(ms)
@@ -307,7 +311,7 @@ template<int STAGE>
 void launch_stage(int minb, int grid, cudaStream_t st, const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, const StageArgs &a, const StageQueues &Q)
 {
 	// second instantiation for scenes without specular materials: see y4_vertex
-	if(sc.has_specular || STAGE == kStLevelFinish)
+	if(sc.has_specular || STAGE == kStLevelFinish || STAGE >= kStPrimary3)
 	{
 		// the general variant carries more live state: its own register budget (env Y4GPU_PT_GENERAL_MIN_BLOCKS, default = the plain one's)
 		static const int general_minb = getenv("Y4GPU_PT_GENERAL_MIN_BLOCKS") ? atoi(getenv("Y4GPU_PT_GENERAL_MIN_BLOCKS")) : 0;
@@ -318,7 +322,7 @@ void launch_stage(int minb, int grid, cudaStream_t st, const Y4PtScene &sc, cons
 	}
 	else
 	{
-		constexpr int S = STAGE == kStLevelFinish ? kStPath : STAGE;      // (never launched without specular materials)
+		constexpr int S = (STAGE == kStLevelFinish || STAGE >= kStPrimary3) ? kStPath : STAGE;      // (never launched without specular materials)
 		if(minb >= 4) k_pt_stage<S, 4, false><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
 		else if(minb == 3) k_pt_stage<S, 3, false><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
 		else k_pt_stage<S, 2, false><<<grid, kPtThreads, 0, st>>>(sc, W, ps, a, Q);
@@ -335,6 +339,24 @@ void pt_free_wave(Y4Pt::Lane &L)
 {
 	cudaFree(L.mem); L.mem = nullptr; L.cap = 0;
 	cudaFree(L.cmem); L.cmem = nullptr; L.ccap = 0;
+	cudaFree(L.tmem); L.tmem = nullptr; L.tcap = 0; L.tdepth = 0;
+}
+
+// Stack of the ray-tree mode: `depth` entries per pixel-sample slot (a depth-first walk of a binary tree with `depth` levels
+// never has more pending siblings than that).
+int pt_alloc_tree(y4gpu_ctx *ctx, Y4Pt::Lane &L, uint32_t cap, int depth)
+{
+	if(cap > L.tcap || depth > L.tdepth)
+	{
+		cudaFree(L.tmem); L.tmem = nullptr; L.tcap = 0; L.tdepth = 0;
+		Y4_CUDA(ctx, cudaMalloc(&L.tmem, (size_t) cap * depth * 48 + (size_t) cap * 4 + 256));
+		L.tcap = cap; L.tdepth = depth;
+	}
+	char *p = (char *) L.tmem;
+	L.wave.stk_ray = (Y4Ray *) p; p += (size_t) L.tcap * L.tdepth * 32;
+	L.wave.stk_sw = (float *) p; p += (size_t) L.tcap * L.tdepth * 16;
+	L.wave.stk_n = (uint32_t *) p;
+	return Y4GPU_OK;
 }
 
 // The two dense path waves of the compacting bounce loop: only the fields the bounce loop moves (308 B per slot and wave).
@@ -506,7 +528,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	if(params->bounces < 1 || params->bounces > 11) { ctx->err = "bounces must be 1..11 (sample dimensions 4*depth+4 < 50)"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(params->path_samples < 0 || params->width < 1 || params->height < 1) { ctx->err = "bad path_samples / film size"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_mat; ++i)
-		if(mats[i].type < Y4GPU_MAT_SHINYDIFFUSE || mats[i].type > Y4GPU_MAT_MIRROR) { ctx->err = "unsupported material type"; return Y4GPU_ERR_UNSUPPORTED; }
+		if(mats[i].type < Y4GPU_MAT_SHINYDIFFUSE || mats[i].type > Y4GPU_MAT_GLASS) { ctx->err = "unsupported material type"; return Y4GPU_ERR_UNSUPPORTED; }
 	for(uint32_t i = 0; i < n_mat; ++i)
 		if(mats[i].layer_count < 0 || (mats[i].layer_count > 0 && (mats[i].layer_first < 0 || !ctx->pt || (uint32_t) (mats[i].layer_first + mats[i].layer_count) > ctx->pt->n_layers)))
 		{ ctx->err = "material refers to layers that were not set (call y4gpu_pt_set_textures first)"; return Y4GPU_ERR_ARG; }
@@ -536,12 +558,17 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		if(mats[m].type == Y4GPU_MAT_MIRROR && !sc.has_specular) sc.has_specular = 1;
 		// translucency needs the full material code (the no-specular kernel variant folds it away), not the ray levels
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].translucency > 0.00001f && !sc.has_specular) sc.has_specular = 1;
-		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f)) sc.has_specular = 2;
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f) && sc.has_specular < 2) sc.has_specular = 2;
+		// two specular children per vertex (glass: reflection + refraction): recursiveRaytrace is a tree, walked depth first with a
+		// per-pixel-sample stack (y4_stage_primary3 / y4_stage_finish3)
+		if(mats[m].type == Y4GPU_MAT_GLASS) sc.has_specular = 3;
 	}
+	if(sc.has_specular == 3 && params->transp_background) { ctx->err = "transparent background together with glass / mirror + transparency materials is not supported (alpha of a ray tree)"; return Y4GPU_ERR_UNSUPPORTED; }
 	for(uint32_t m = 0; m < n_mat; ++m)
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].transparency > 0.00001f)
 		{
 			// reflect + refract at one vertex = two child rays (a tree, not a chain); filtered shadows need the blockers' colours
+			// (the ray tree could walk reflect + refract, but ShinyDiffuseMaterial::sample with all four components is not restated: y4_mat_sample keeps mirror / transparency in one slot)
 			if(mats[m].specular_reflect > 0.00001f) { ctx->err = "shinydiffusemat with both specular_reflect and transparency is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 			// filtered shadows take one getTransparency colour per material: a textured diffuse colour would need the blocker's surface point
 			if(params->transp_shadows && mats[m].layer_count > 0) { ctx->err = "textured transparent materials with transpShad are not supported"; return Y4GPU_ERR_UNSUPPORTED; }
@@ -549,7 +576,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	// no_recursive makes a mirror hit start sub-paths AND recurse: two branches per vertex, which the linear ray-level chain does not cover
 	bool chain_mats = false;
 	for(uint32_t m = 0; m < n_mat; ++m)
-		chain_mats = chain_mats || mats[m].type == Y4GPU_MAT_MIRROR || (mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f));
+		chain_mats = chain_mats || mats[m].type == Y4GPU_MAT_MIRROR || mats[m].type == Y4GPU_MAT_GLASS || (mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f));
 	if(chain_mats && sc.no_recursive) { ctx->err = "no_recursive with mirror materials / specular_reflect is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 	// object lights need the general kernel variant as well (not the ray levels)
 	for(uint32_t l = 0; l < n_light; ++l) if(lights[l].type == Y4GPU_LIGHT_OBJECT && !sc.has_specular) sc.has_specular = 1;
@@ -851,7 +878,8 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	const bool prof = pt->params.profile != 0;
 	// lanes: consecutive waves alternate between two streams (profile mode times kernels one by one: single lane)
 	const uint64_t n_waves_total = total ? (total + wave_size - 1) / wave_size : 0;
-	const int n_lanes = (pt->n_lanes > 1 && !prof && n_waves_total > 1) ? (int) (n_waves_total < (uint64_t) pt->n_lanes ? n_waves_total : (uint64_t) pt->n_lanes) : 1;
+	const bool tree = sc.has_specular == 3;       // two children per vertex: the host reads a queue length back after every run (one lane)
+	const int n_lanes = (pt->n_lanes > 1 && !prof && n_waves_total > 1 && !tree) ? (int) (n_waves_total < (uint64_t) pt->n_lanes ? n_waves_total : (uint64_t) pt->n_lanes) : 1;
 	pt->lanes[0].stream = st;
 	if(n_lanes > 1 && !pt->ev_fork) Y4_CUDA(ctx, cudaEventCreateWithFlags(&pt->ev_fork, cudaEventDisableTiming));
 	for(int l = 1; l < n_lanes; ++l)
@@ -860,6 +888,8 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		if(!pt->lanes[l].done) Y4_CUDA(ctx, cudaEventCreateWithFlags(&pt->lanes[l].done, cudaEventDisableTiming));
 	}
 	for(int l = 0; l < n_lanes; ++l) { const int rc = pt_alloc_wave(ctx, pt->lanes[l], wave_size); if(rc) return rc; }
+	const int tree_depth = (sc.raydepth < 19 ? sc.raydepth : 19) + 2;
+	if(tree) for(int l = 0; l < n_lanes; ++l) { const int rc = pt_alloc_tree(ctx, pt->lanes[l], wave_size, tree_depth); if(rc) return rc; }
 	// the compacting bounce loop carries no incoming ray / hit for extra light samples at a path vertex (k > 0): lights with one sample only
 	const bool compact = pt->compact != 0 && pt->max_light_samples == 1 && sc.n_paths > 0;
 	if(compact)
@@ -889,7 +919,9 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	const uint64_t n_waves = total ? (total + wave_size - 1) / wave_size : 0;
 	const size_t n_levels = (size_t) (sc.has_specular ? (sc.raydepth < 20 ? sc.raydepth : 20) : 0) + 1;
 	const size_t per_level = 6 + 2 * all_lk.size() + (size_t) sc.n_paths * (2 + ((size_t) sc.bounces + 1) * (4 + 2 * (size_t) max_ls));
-	const size_t per_wave = sc.has_specular == 2 ? n_levels * per_level : per_level + 2 * n_levels;
+	// tree mode: one run per tree node a pixel-sample visits, at most 2^(raydepth + 1) - 1 (capped: deeper trees fail the pass)
+	const size_t tree_runs = tree ? (sc.raydepth < 7 ? ((size_t) 2 << sc.raydepth) : 256) : 0;
+	const size_t per_wave = tree ? tree_runs * (per_level + 2) : (sc.has_specular == 2 ? n_levels * per_level : per_level + 2 * n_levels);
 	const size_t need = 8 + n_waves * per_wave;
 	if(need > pt->counters_cap)
 	{
@@ -953,9 +985,11 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		// anything is estimated and their end points share one run of the estimate below.  A shinydiffuse vertex with a mirror
 		// component needs its own estimate first: then every level is one run (camera-hit step, estimate, level-finish stage).
 		const int max_level = (sc.has_specular && sc.raydepth > 0) ? (sc.raydepth < 19 ? sc.raydepth : 19) : 0;
-		const bool level_runs = sc.has_specular == 2;
+		const bool level_runs = sc.has_specular >= 2;
 		uint32_t *next_level_count = nullptr;                    // length of the queue of rays reflected into `level + 1`
-		for(int level = 0; level <= (level_runs ? max_level : 0); ++level)
+		// tree mode: `level` counts RUNS (one tree node per pixel-sample and run; every entry carries its own ray level in W.sw),
+		// the loop ends when no pixel-sample has a tree ray left
+		for(int level = 0; level <= (tree ? (int) tree_runs : (level_runs ? max_level : 0)); ++level)
 		{
 		a = {0, -1, -1, -1, -1, 0, 0, level};
 		Q = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -974,8 +1008,9 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		new_queue_pair(2, 1, n_hit0, Q.sh_count);
 		Q.out_q = lane.q_hit0; Q.out_count = n_hit0; Q.sh_q = lane.q_shadow;
 		a.l = all_lk.empty() ? -1 : all_lk[0].first;
-		if(level < max_level) { Q.spec_q = lane.q_spec[(level + 1) & 1]; Q.spec_count = next_level_count = new_queue_count(4); }
-		Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
+		if(level < max_level || tree) { Q.spec_q = lane.q_spec[(level + 1) & 1]; Q.spec_count = next_level_count = new_queue_count(4); }
+		if(tree) Y4_PT_LAUNCH(3, launch_stage<kStPrimary3>(stage_minb, grid, st, dsc, W, ps, a, Q));
+		else Y4_PT_LAUNCH(3, launch_stage<kStPrimary>(stage_minb, grid, st, dsc, W, ps, a, Q));
 		for(int lv = 1; !level_runs && lv <= max_level; ++lv)
 		{
 			const uint32_t *in_q = Q.spec_q, *in_count = Q.spec_count;
@@ -1073,7 +1108,22 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 			}
 		}
 		W.ray = ray_buf[0]; W.ray_next = ray_buf[1];
-		if(level_runs && level < max_level)
+		if(tree)
+		{
+			// close the vertices that were estimated, then see whether any pixel-sample still has a tree ray to trace
+			Q = {lane.q_hit0, n_hit0, nullptr, nullptr, nullptr, nullptr, lane.q_spec[(level + 1) & 1], next_level_count};
+			Y4_PT_LAUNCH(3, launch_stage<kStFinish3>(stage_minb, grid, st, dsc, W, ps, a, Q));
+			const size_t slot = (size_t) (reinterpret_cast<unsigned long long *>(next_level_count) - pt->d_counters);
+			Y4_CUDA(ctx, cudaMemcpyAsync(pt->h_counters + slot, pt->d_counters + slot, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+			Y4_CUDA(ctx, cudaStreamSynchronize(st));
+			if((uint32_t) pt->h_counters[slot] == 0u) break;
+			if(level == (int) tree_runs)
+			{
+				ctx->err = "ray tree of a pixel-sample has more nodes than the run limit (raydepth too high for the tree mode)";
+				return Y4GPU_ERR_UNSUPPORTED;
+			}
+		}
+		else if(level_runs && level < max_level)
 		{
 			Q = {lane.q_hit0, n_hit0, nullptr, nullptr, nullptr, nullptr, lane.q_spec[(level + 1) & 1], next_level_count};
 			a.level = level;

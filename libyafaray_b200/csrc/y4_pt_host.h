@@ -99,6 +99,16 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 		o.bsdf_flags = Y4_BSDF_SPECULAR;
 		return o;
 	}
+	if(m.type == Y4GPU_MAT_GLASS)                          // GlassMaterial ctor (material_glass.cc:35-50)
+	{
+		// `color` arrives as the constructor's filt_c = filt * filter_color + Rgb(1.f - filt) (factory, :326: `filt` is a double
+		// parameter, so the caller forms it like the reference does and nothing is rounded twice here)
+		o.color = c3(m.color[0], m.color[1], m.color[2]);
+		o.mirror_color = c3(m.mirror_color[0], m.mirror_color[1], m.mirror_color[2]);
+		o.ior = m.ior;
+		o.bsdf_flags = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT | Y4_BSDF_TRANSMIT;      // BsdfFlags::AllSpecular
+		return o;
+	}
 	o.color = c3(m.color[0], m.color[1], m.color[2]);
 	o.layer_first = m.layer_first; o.layer_count = m.layer_count; o.emit_strength = m.emit;
 	o.emit = c3(m.emit * m.color[0], m.emit * m.color[1], m.emit * m.color[2]);

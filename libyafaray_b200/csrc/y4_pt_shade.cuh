@@ -119,6 +119,70 @@ Y4_HD V3 y4_reflect_dir(const V3 n, const V3 v)
 	return v3(xsub(xmul(k, n.x), v.x), xsub(xmul(k, n.y), v.y), xsub(xmul(k, n.z), v.z));
 }
 
+// ---- glass (src/material/material_glass.cc) ------------------------------------------------------------------
+// Vec3::refract (src/geometry/vector.cc:64-86)
+Y4_HD bool y4_refract(const V3 n, const V3 wi, V3 &wo, float ior)
+{
+	V3 nn = n;
+	float eta = ior;
+	const V3 i = xneg(wi);
+	float cos_v_n = xdot(wi, n);
+	if(cos_v_n < 0.f) { nn = xneg(n); cos_v_n = -cos_v_n; }
+	else eta = xdiv(1.f, ior);
+	const float k = xsub(1.f, xmul(xmul(eta, eta), xsub(1.f, xmul(cos_v_n, cos_v_n))));
+	if(k <= 0.f) return false;
+	const float f = xsub(xmul(eta, cos_v_n), xsqrt(k));
+	wo = xnormalize(xadd3(xscale(i, eta), xscale(nn, f)));
+	return true;
+}
+// Vec3::fresnel (vector.cc:88-115)
+Y4_HD void y4_fresnel(const V3 i, const V3 n, float ior, float &kr, float &kt)
+{
+	const V3 nn = xdot(i, n) < 0.f ? xneg(n) : n;
+	const float c = xdot(i, nn);
+	float g = xsub(xadd(xmul(ior, ior), xmul(c, c)), 1.f);
+	g = g <= 0.f ? 0.f : xsqrt(g);
+	const float aux = xmul(c, xadd(g, c));
+	const float gmc = xsub(g, c), gpc = xadd(g, c), am = xsub(aux, 1.f), ap = xadd(aux, 1.f);
+	kr = xmul(xdiv(xmul(xmul(0.5f, gmc), gmc), xmul(gpc, gpc)), xadd(1.f, xdiv(xmul(am, am), xmul(ap, ap))));
+	kt = kr < 1.f ? xsub(1.f, kr) : 0.f;
+}
+// the shading normal glass works with (GlassMaterial::sample :62-66 with a double literal, getSpecular :217-226 with a float one)
+Y4_HD V3 y4_glass_normal(const Y4Surf &sp, const V3 wo, bool double_literal)
+{
+	const bool outside = xdot(sp.ng, wo) > 0.f;
+	const float cos_wo_n = xdot(sp.n, wo);
+	if(outside ? (cos_wo_n >= 0.f) : (cos_wo_n <= 0.f)) return sp.n;
+	const float k = double_literal ? (float) xdmul(1.00001, (double) cos_wo_n) : xmul(1.00001f, cos_wo_n);
+	return xnormalize(xsub3(sp.n, xscale(wo, k)));
+}
+// Vec3::reflect (vector.h:227-232) applied to wo
+Y4_HD V3 y4_reflect(const V3 v, const V3 n)
+{
+	const float vn = xmul(2.f, xadd(xadd(xmul(v.x, n.x), xmul(v.y, n.y)), xmul(v.z, n.z)));
+	return v3(xsub(xmul(vn, n.x), v.x), xsub(xmul(vn, n.y), v.y), xsub(xmul(vn, n.z), v.z));
+}
+// GlassMaterial::getSpecular (:215-280; no dispersion): reflected and / or refracted continuation with its colour.
+// ray_level = the level recursiveRaytrace was called with (integrate()'s level + 1).
+struct Y4Specular { bool reflect, refract; V3 reflect_dir, refract_dir; C3 reflect_col, refract_col; };
+Y4_HD Y4Specular y4_glass_specular(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, int ray_level)
+{
+	Y4Specular s; s.reflect = false; s.refract = false;
+	s.reflect_dir = s.refract_dir = v3(0.f, 0.f, 1.f); s.reflect_col = s.refract_col = c3f(0.f);
+	const bool outside = xdot(sp.ng, wo) > 0.f;
+	const V3 n = y4_glass_normal(sp, wo, false);
+	V3 refdir;
+	if(y4_refract(n, wo, refdir, m.ior))
+	{
+		float kr, kt;
+		y4_fresnel(wo, n, m.ior, kr, kt);
+		s.refract = true; s.refract_col = cscale(m.color, kt); s.refract_dir = refdir;
+		if(outside || ray_level < 3) { s.reflect = true; s.reflect_dir = y4_reflect(wo, n); s.reflect_col = cscale(m.mirror_color, kr); }    // Rgb * float: {r * f, ...}
+	}
+	else { s.reflect = true; s.reflect_col = m.mirror_color; s.reflect_dir = y4_reflect(wo, n); }      // total inner reflection
+	return s;
+}
+
 // Material::sample -> returns scolor; wi, w, pdf, sampled (false == BsdfFlags::None) are outputs.
 // `w` is left untouched when nothing is sampled (the reference leaves its out-parameter alone too).
 Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, float s1, float s2, uint32_t flags,
@@ -131,6 +195,25 @@ Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, flo
 		wi = y4_reflect_dir(sp.n, wo);
 		sampled = true; w = 1.f; specular = true;
 		return cscale(m.color, xdiv(1.f, fabsf(xdot(sp.n, wi))));
+	}
+	if(m.type == Y4GPU_MAT_GLASS)                          // GlassMaterial::sample (:62-203), branch without dispersion, tm_flags_ = Specular | Transmit
+	{
+		if(!(flags & Y4_BSDF_SPECULAR)) return c3f(0.f);
+		const V3 ng = y4_glass_normal(sp, wo, true);
+		const uint32_t tm = Y4_BSDF_SPECULAR | Y4_BSDF_TRANSMIT, rm = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT;
+		V3 refdir;
+		pdf = 1.f;
+		if(y4_refract(ng, wo, refdir, m.ior))
+		{
+			float kr, kt;
+			y4_fresnel(wo, ng, m.ior, kr, kt);
+			const float p_kr = (float) xdadd(0.01, xdmul(0.99, (double) kr)), p_kt = (float) xdadd(0.01, xdmul(0.99, (double) kt));
+			if(s1 < p_kt && (flags & tm) == tm) { wi = refdir; pdf = p_kt; sampled = true; specular = true; w = 1.f; return m.color; }
+			if((flags & rm) == rm) { wi = y4_reflect(wo, ng); pdf = p_kr; sampled = true; specular = true; w = 1.f; return m.mirror_color; }
+		}
+		else if((flags & rm) == rm) { wi = y4_reflect(wo, ng); sampled = true; specular = true; w = 1.f; return c3f(1.f); }
+		pdf = 0.f;
+		return c3f(0.f);
 	}
 	const float cos_ng_wo = xdot(sp.ng, wo);
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);

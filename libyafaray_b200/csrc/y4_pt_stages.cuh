@@ -34,6 +34,11 @@ struct Y4PtWave
 	Y4Ray *ray0;           // [n] ray_level > 0 (Y4_PF_SPEC): the reflected ray that reached the vertex integrate() works on
 	float *acc;            // [n*4] Y4_PF_ACC: radiance of the upper ray levels, already weighted
 	float *sw;             // [n*4] Y4_PF_SPEC: product of the reflection colours down the mirror chain (xyz), ray level (w, int bits)
+	// ray TREE (has_specular == 3: glass, or shinydiffusemat with mirror AND transparency -- two children per vertex): the
+	// pending sibling branches of a pixel-sample, depth first: entry k of slot i at [k * n + i]
+	Y4Ray *stk_ray;        // [depth * n]
+	float *stk_sw;         // [depth * n * 4] branch weight (xyz), ray level (w, int bits)
+	uint32_t *stk_n;       // [n] entries on the stack
 };
 
 struct Y4PtPass
@@ -697,6 +702,156 @@ Y4_HD uint32_t y4_stage_level_finish(const Y4PtScene &sc, const Y4PtWave &W, con
 	st4(W.sw, i, f4(w.r, w.g, w.b, y4_u2f((uint32_t) (level + 1))));
 	W.flags[i] = Y4_PF_SPEC | Y4_PF_ACC;
 	return Y4_PUSH_SPEC;
+}
+
+// ==== ray tree: recursiveRaytrace with up to two children per vertex (integrator_montecarlo.cc:918-968) ====================
+// A pixel-sample walks its tree depth first.  Every vertex integrate() visits contributes (product of the specular colours
+// down its branch) x (its own radiance: emission + light estimates + sub-paths, or the background); the contributions are
+// summed into W.acc as the walk goes (the reference unwinds the same products and sums from the leaves up: <= 1 ulp per
+// level apart).  One child continues in the slot (W.ray0 / W.sw), the sibling waits on the stack.
+Y4_HD void y4_tree_fold(const Y4PtWave &W, uint32_t i, uint32_t &f, C3 rad)
+{
+	if(f & Y4_PF_SPEC) rad = cmul(rad, ld3(W.sw, i));
+	if(f & Y4_PF_ACC) rad = cadd(ld3(W.acc, i), rad);
+	st3(W.acc, i, rad);
+	f |= Y4_PF_ACC;
+}
+// the vertex at (p, level) is done and has n_children (0..2) specular continuations; returns Y4_PUSH_SPEC while the
+// pixel-sample has a ray to trace, 0 when its tree is finished (then W.col / W.flags are what the splat expects)
+Y4_HD uint32_t y4_tree_next(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t f, int level, const V3 p, int n_children, const V3 *dir, const C3 *col)
+{
+	const uint32_t n = W.n;
+	const bool has_sw = (f & Y4_PF_SPEC) != 0;
+	const C3 sw = has_sw ? ld3(W.sw, i) : c3f(1.f);
+	const float lvl = y4_u2f((uint32_t) (level + 1));
+	uint32_t k = W.stk_n[i];
+	if(n_children == 2)
+	{
+		const C3 w1 = has_sw ? cmul(sw, col[1]) : col[1];
+		st_ray(W.stk_ray, k * n + i, y4_mk_ray(p, sc.ray_min_dist, dir[1], -1.f));
+		st4(W.stk_sw, k * n + i, f4(w1.r, w1.g, w1.b, lvl));
+		W.stk_n[i] = ++k;
+	}
+	if(n_children >= 1)
+	{
+		const C3 w0 = has_sw ? cmul(sw, col[0]) : col[0];
+		st_ray(W.ray0, i, y4_mk_ray(p, sc.ray_min_dist, dir[0], -1.f));
+		st4(W.sw, i, f4(w0.r, w0.g, w0.b, lvl));
+		W.flags[i] = Y4_PF_SPEC | (f & Y4_PF_ACC);
+		return Y4_PUSH_SPEC;
+	}
+	if(k > 0)
+	{
+		--k;
+		W.stk_n[i] = k;
+		st_ray(W.ray0, i, ld_ray(W.stk_ray, k * n + i));
+		st4(W.sw, i, ld4(W.stk_sw, k * n + i));
+		W.flags[i] = Y4_PF_SPEC | (f & Y4_PF_ACC);
+		return Y4_PUSH_SPEC;
+	}
+	st4(W.col, i, f4(0.f, 0.f, 0.f, 1.f));          // everything is in W.acc (alpha 1: transparent backgrounds are refused in tree mode)
+	W.flags[i] = f & Y4_PF_ACC;
+	return 0u;
+}
+// the specular continuations of a vertex: mirror, glass, shinydiffusemat (mirror and / or transparency component)
+Y4_HD int y4_tree_children(const Y4Vertex &vx, int level, V3 *dir, C3 *col)
+{
+	const Y4PtMaterial &m = vx.m;
+	int nc = 0;
+	if(m.type == Y4GPU_MAT_MIRROR)
+	{
+		dir[0] = y4_reflect_dir(y4_face_forward(vx.sp.ng, vx.sp.n, vx.wo), vx.wo); col[0] = m.color;     // MirrorMaterial::getSpecular
+		return 1;
+	}
+	if(m.type == Y4GPU_MAT_GLASS)
+	{
+		const Y4Specular s = y4_glass_specular(m, vx.sp, vx.wo, level + 1);
+		if(s.reflect) { dir[nc] = s.reflect_dir; col[nc] = s.reflect_col; ++nc; }
+		if(s.refract) { dir[nc] = s.refract_dir; col[nc] = s.refract_col; ++nc; }
+		return nc;
+	}
+	if(m.type != Y4GPU_MAT_SHINYDIFFUSE) return 0;
+	// ShinyDiffuseMaterial::getSpecular (material_shiny_diffuse.cc:399-439)
+	const bool backface = xdot(vx.wo, vx.sp.ng) < 0.f;
+	const V3 n = backface ? xneg(vx.sp.n) : vx.sp.n, ng = backface ? xneg(vx.sp.ng) : vx.sp.ng;
+	const float kr = y4_fresnel_kr(m, vx.wo, n);
+	if(m.is_mirror)
+	{
+		V3 d = y4_reflect(vx.wo, n);
+		const float cos_wi_ng = xdot(d, ng);
+		if((double) cos_wi_ng < 0.01)
+		{
+			const float k = (float) (0.01 - (double) cos_wi_ng);
+			d = xnormalize(v3(xadd(d.x, xmul(k, ng.x)), xadd(d.y, xmul(k, ng.y)), xadd(d.z, xmul(k, ng.z))));
+		}
+		dir[nc] = d; col[nc] = cscale(m.mirror_color, xmul(m.mirror_strength, kr)); ++nc;
+	}
+	if(m.is_transparent)
+	{
+		dir[nc] = xneg(vx.wo);
+		col[nc] = cscale(y4_shiny_tcol(m), xmul(xsub(1.f, xmul(m.is_mirror ? m.mirror_strength : 0.f, kr)), m.transparency_strength)); ++nc;
+	}
+	return nc;
+}
+
+// camera-ray / tree-ray hit in tree mode.  run == 0: dense over the wave (camera rays), else over the queue of pending tree rays.
+// Push bits: Y4_PUSH_PATH -> the vertex needs an estimate (hit0 queue; y4_stage_finish3 closes it); Y4_PUSH_SPEC -> a tree ray to trace.
+Y4_HD uint32_t y4_stage_primary3(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l0, int run)
+{
+	uint32_t f = run > 0 ? (W.flags[i] & (uint32_t) (Y4_PF_SPEC | Y4_PF_ACC)) : 0u;
+	if(run == 0) W.stk_n[i] = 0u;
+	const int level = (f & Y4_PF_SPEC) ? (int) y4_f2u(ld4(W.sw, i).w) : 0;
+	const Y4Hit h = ld_hit(W.hit, i);
+	const Y4Ray r = (f & Y4_PF_SPEC) ? ld_ray(W.ray0, i) : ld_ray(W.ray, i);
+	V3 dir[2]; C3 col[2];
+	if(h.prim < 0)
+	{
+		y4_tree_fold(W, i, f, y4_background(sc, v3(r.dx, r.dy, r.dz)));
+		return y4_tree_next(sc, W, i, f, level, v3(0.f, 0.f, 0.f), 0, dir, col);
+	}
+	st_hit(W.hit0, i, h);
+	const Y4Vertex vx = y4_vertex<true>(sc, r, h);
+	const bool deeper = level + 1 <= sc.raydepth && level + 1 < 20;
+	if(vx.m.type == Y4GPU_MAT_MIRROR || vx.m.type == Y4GPU_MAT_GLASS)
+	{
+		// no Diffuse, no Emit: integrate() returns recursiveRaytrace's share only
+		const int nc = deeper ? y4_tree_children(vx, level, dir, col) : 0;
+		return y4_tree_next(sc, W, i, f, level, vx.sp.p, nc, dir, col);
+	}
+	C3 c = c3f(0.f);
+	if(vx.m.bsdf_flags & Y4_BSDF_EMIT) c = cadd(c, y4_mat_emit(vx.m, vx.sp, vx.wo));
+	st4(W.col, i, f4(c.r, c.g, c.b, 1.f));
+	st3(W.pcol, i, c3f(0.f));
+	st4(W.lsamp, i, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
+	f |= Y4_PF_HIT0;
+	if((vx.m.is_mirror || vx.m.is_transparent) && deeper) f |= Y4_PF_RECURSE;
+	if(vx.m.bsdf_flags & Y4_BSDF_DIFFUSE) f |= Y4_PF_DIRECT;
+	if(sc.n_paths > 0 && (vx.m.bsdf_flags & Y4_BSDF_DIFFUSE)) f |= Y4_PF_PATHS;
+	uint32_t push = 0u;
+	if(l0 >= 0) push |= y4_pt_direct<true>(sc, W, ps, i, f, true, l0, 0, vx, f4(0.f, 0.f, y4_u2f(0xffffffffu), y4_u2f(0xffffffffu)));
+	W.flags[i] = f;
+	return push | Y4_PUSH_PATH;          // every such vertex goes through y4_stage_finish3 (which also handles "nothing to estimate")
+}
+
+// the estimate of a tree vertex is complete: fold it in, spawn its specular children (shinydiffusemat), go on with the tree
+Y4_HD uint32_t y4_stage_finish3(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i)
+{
+	uint32_t f = W.flags[i];
+	const C3 rad = y4_level_radiance(sc, W, i, f, ld4(W.col, i));
+	const int level = (f & Y4_PF_SPEC) ? (int) y4_f2u(ld4(W.sw, i).w) : 0;
+	const bool recurse = (f & Y4_PF_RECURSE) != 0;
+	uint32_t g = f & (uint32_t) (Y4_PF_SPEC | Y4_PF_ACC);
+	y4_tree_fold(W, i, g, rad);
+	V3 dir[2]; C3 col[2];
+	int nc = 0;
+	V3 p = v3(0.f, 0.f, 0.f);
+	if(recurse)
+	{
+		const Y4Vertex vx = y4_vertex<true>(sc, y4_level_ray<true>(sc, W, ps, i, f, W.pix[i], W.samp[i]), ld_hit(W.hit0, i));
+		nc = y4_tree_children(vx, level, dir, col);
+		p = vx.sp.p;
+	}
+	return y4_tree_next(sc, W, i, g, level, p, nc, dir, col);
 }
 
 // ---- stage: close the pixel-sample and splat it into the film ----------------------------------------

@@ -58,6 +58,8 @@ struct Y4PtMaterial
 	// shinydiffusemat's straight-through transparency component (components_[1]): transparency, transmit_filter
 	int is_transparent; float transparency_strength, transmit_filter;
 	int is_translucent; float translucency_strength;              // components_[2]: diffuse transmission
+	// glass (material_glass.cc): ior_, filter_color_ = filt * filter_color + (1 - filt) (kept in `color`), specular_reflection_color_ (in mirror_color)
+	float ior;
 };
 
 // ImageTexture state (texture_image.cc:476-597) + texels as Image::getColor returns them

@@ -233,6 +233,18 @@ class Interface:
                 p["_diffuse_chain"] = self._diffuse_chain(name, p, [dict(e) for e in self.eparams])
         elif t == "mirror":            # MirrorMaterial::factory reads `color` and `reflect` only (material_glass.cc:453-461)
             p = {"type": "mirror", "color": p.get("color", (1.0, 1.0, 1.0, 1.0)), "reflect": p.get("reflect", 1.0)}
+        elif t == "glass":             # GlassMaterial::factory (material_glass.cc:290-433)
+            if float(p.get("dispersion_power", 0.0)) > 0.0:
+                raise Y4Error(f"glass '{name}': dispersion is not supported by the GPU back end")
+            if p.get("fake_shadows", False):
+                raise Y4Error(f"glass '{name}': fake_shadows is not supported by the GPU back end")
+            ab = p.get("absorption", (1.0, 1.0, 1.0, 1.0))
+            if min(ab[:3]) < 1.0:
+                raise Y4Error(f"glass '{name}': absorption (a volume handler) is not supported by the GPU back end")
+            if float(p.get("wireframe_amount", 0.0)) != 0.0 or float(p.get("samplingfactor", 1.0)) != 1.0 or int(p.get("additionaldepth", 0)) != 0:
+                raise Y4Error(f"glass '{name}': wireframe / samplingfactor / additionaldepth are not supported by the GPU back end")
+            if any(k.endswith("_shader") for k in p):
+                raise Y4Error(f"glass '{name}': shader nodes are not supported by the GPU back end")
         elif t != "light_mat":
             raise Y4Error(f"material type '{t}' is not supported by the GPU back end")
         self.materials[name] = p
@@ -538,6 +550,13 @@ class Interface:
                 m.type, m.emit, m.double_sided = _lib.MAT_LIGHT, float(p.get("power", 1.0)), int(p.get("double_sided", False))
             elif p["type"] == "mirror":
                 m.type, m.diffuse_reflect = _lib.MAT_MIRROR, float(p.get("reflect", 1.0))
+            elif p["type"] == "glass":
+                m.type, m.ior = _lib.MAT_GLASS, float(p.get("IOR", 1.4))
+                # filt * filt_col + Rgb(1.f - filt) with `filt` a double parameter (material_glass.cc:326): float products, the offset rounded once
+                filt = float(p.get("transmit_filter", 0.0))
+                fc = p.get("filter_color", (1.0, 1.0, 1.0, 1.0))
+                m.color[:] = [float(np.float32(np.float32(filt) * np.float32(fc[k])) + np.float32(1.0 - filt)) for k in range(3)]
+                m.mirror_color[:] = p.get("mirror_color", (1.0, 1.0, 1.0, 1.0))[:3]
             else:
                 m.type, m.diffuse_reflect, m.emit = _lib.MAT_SHINYDIFFUSE, float(p.get("diffuse_reflect", 1.0)), float(p.get("emit", 0.0))
                 m.specular_reflect, m.fresnel_effect, m.ior = float(p.get("specular_reflect", 0.0)), int(p.get("fresnel_effect", False)), float(p.get("IOR", 1.33))
@@ -599,7 +618,7 @@ class Interface:
         pr.transp_background = int(integ.get("bg_transp", False))
         if integ.get("transpShad", False) and any(float(self.materials[n].get("transparency", 0.0)) > 0.00001 and n in chain_of for n in mat_names):
             raise Y4Error("textured transparent materials with transpShad are not supported by the GPU back end")
-        if pr.no_recursive and any(self.materials[n]["type"] == "mirror" or float(self.materials[n].get("specular_reflect", 0.0)) > 0.00001
+        if pr.no_recursive and any(self.materials[n]["type"] in ("mirror", "glass") or float(self.materials[n].get("specular_reflect", 0.0)) > 0.00001
                                    or float(self.materials[n].get("transparency", 0.0)) > 0.00001 for n in mat_names):
             raise Y4Error("no_recursive with mirror materials / specular_reflect is not supported by the GPU back end")
         pr.raydepth, pr.transp_refracted_background = int(integ.get("raydepth", 5)), int(integ.get("bg_transp_refract", False))

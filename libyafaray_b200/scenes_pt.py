@@ -84,7 +84,7 @@ def _uv_sphere(centre, radius, nu, nv):
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
                 oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None,
-                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None, mesh_light=None):
+                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None, mesh_light=None, glass=None, box_lift=0.0):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front.
     mirror: {"objects": subset of ("tall", "short", "back", "left", "sphere"), "color": rgb, "reflect": r} -> those objects get a
@@ -109,7 +109,17 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         api.paramsSetColor("color", *mirror.get("color", (0.9, 0.9, 0.9)), 1.0)
         api.paramsSetFloat("reflect", mirror.get("reflect", 1.0))
         api.createMaterial("mirror")
-    mat = lambda obj, default: "mirror" if obj in mirrored else default
+    # glass: {"objects": subset of ("tall", "short", "sphere"), "IOR", "filter_color", "transmit_filter", "mirror_color"} -> a `glass` material
+    glassy = set((glass or {}).get("objects", ()))
+    if glass:
+        api.paramsClearAll()
+        api.paramsSetString("type", "glass")
+        api.paramsSetFloat("IOR", float(glass.get("IOR", 1.5)))
+        api.paramsSetColor("filter_color", *glass.get("filter_color", (1.0, 1.0, 1.0)), 1.0)
+        api.paramsSetFloat("transmit_filter", float(glass.get("transmit_filter", 0.0)))
+        api.paramsSetColor("mirror_color", *glass.get("mirror_color", (1.0, 1.0, 1.0)), 1.0)
+        api.createMaterial("glass")
+    mat = lambda obj, default: "mirror" if obj in mirrored else ("glass" if obj in glassy else default)
 
     api.startGeometry()
     v, t = _quad((0, 0, 0), (1, 0, 0), (1, 0, 1), (0, 0, 1))
@@ -122,9 +132,11 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     _mesh(api, "d_left", mat("left", "red"), v, t)
     v, t = _quad((1, 0, 0), (1, 1, 0), (1, 1, 1), (1, 0, 1))
     _mesh(api, "e_right", "green", v, t)
-    v, t = _box((0.53, 0.0, 0.53), (0.83, 0.6, 0.83), 18.0, (0.68, 0.0, 0.68))
+    # box_lift: raises the two boxes off the floor (a glass box standing ON the floor has its bottom face coincide with the floor:
+    # rays inside it meet two surfaces at exactly the same t, the documented tie class)
+    v, t = _box((0.53, box_lift, 0.53), (0.83, 0.6, 0.83), 18.0, (0.68, 0.0, 0.68))
     _mesh(api, "f_tall", mat("tall", "white"), v, t)
-    v, t = _box((0.18, 0.0, 0.2), (0.48, 0.3, 0.5), -17.0, (0.33, 0.0, 0.35))
+    v, t = _box((0.18, box_lift, 0.2), (0.48, 0.3, 0.5), -17.0, (0.33, 0.0, 0.35))
     _mesh(api, "g_short", mat("short", "white"), v, t)
     # emitting quad just below the ceiling, facing down; the area light shares its corners
     lx0, lx1, lz0, lz1, ly = 0.37, 0.63, 0.395, 0.605, 0.999

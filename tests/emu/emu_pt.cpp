@@ -126,8 +126,10 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		if(mats[m].type == Y4GPU_MAT_MIRROR && !sc.has_specular) sc.has_specular = 1;
 		// translucency needs the full material code (the no-specular kernel variant folds it away), not the ray levels
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].translucency > 0.00001f && !sc.has_specular) sc.has_specular = 1;
-		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f)) sc.has_specular = 2;
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f) && sc.has_specular < 2) sc.has_specular = 2;
+		if(mats[m].type == Y4GPU_MAT_GLASS) sc.has_specular = 3;      // ray-tree mode, as y4gpu_pt_set_scene
 	}
+	if(sc.has_specular == 3 && params->transp_background) return -3;
 	// object lights need the general kernel variant as well (not the ray levels)
 	for(uint32_t l = 0; l < n_light; ++l) if(lights[l].type == Y4GPU_LIGHT_OBJECT && !sc.has_specular) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
@@ -183,6 +185,10 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	W.col = &col[0].x; W.pcol = &pcol[0].x; W.thr = &thr[0].x; W.lcol = &lcol[0].x; W.acc_a = &acc_a[0].x; W.acc_b = &acc_b[0].x; W.lsamp = &lsamp[0].x; W.pthr = &pthr[0].x;
 	W.ray = ray.data(); W.ray_next = ray2.data(); W.hit = hit.data(); W.hit0 = hit0.data(); W.sray = sray.data(); W.shit = shit.data(); W.scontrib = &scontrib[0].x;
 	W.ray0 = ray0.data(); W.sw = &sw[0].x; W.acc = &acc[0].x;
+	const bool tree = sc.has_specular == 3;
+	const int tree_depth = (sc.raydepth < 19 ? sc.raydepth : 19) + 2;
+	std::vector<Y4Ray> stk_ray(tree ? (size_t) tree_depth * n : 0); std::vector<float4> stk_sw(tree ? (size_t) tree_depth * n : 0); std::vector<uint32_t> stk_n(tree ? n : 0);
+	W.stk_ray = stk_ray.data(); W.stk_sw = tree ? &stk_sw[0].x : nullptr; W.stk_n = stk_n.data();
 	Y4PtPass ps; ps.n_samples = n_samples; ps.pass_offs = (uint32_t) offset + sc.base_sampling_offset; ps.aa_pass = aa_pass;
 	for(uint32_t i = 0; i < n; ++i) { pix[i] = pixel_list ? pixel_list[i / ns_local] : i / ns_local; samp[i] = (uint32_t) shard_index + (i % ns_local) * (uint32_t) shard_count; }
 	const int shadow_kind = params->transp_shadows ? Y4_TRACE_TSHADOW : Y4_TRACE_SHADOW;
@@ -197,15 +203,15 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	std::vector<uint32_t> q_spec, q_spec_next;
 	auto primary = [&](uint32_t i, int level)
 	{
-		const uint32_t p = y4_stage_primary(sc, W, ps, i, l0, level);
+		const uint32_t p = tree ? y4_stage_primary3(sc, W, ps, i, l0, level) : y4_stage_primary(sc, W, ps, i, l0, level);
 		push(p, i, n, &q_hit0, &q_shadow);
 		if(p & Y4_PUSH_SPEC) q_spec_next.push_back(i);
 	};
 	// ray levels, as y4gpu_pt_render_pass: whole mirror chains inside the camera-hit step when only pure mirrors exist,
 	// one estimate per level when shinydiffuse materials have a mirror component
 	const int max_level = (sc.has_specular && sc.raydepth > 0) ? (sc.raydepth < 19 ? sc.raydepth : 19) : 0;
-	const bool level_runs = sc.has_specular == 2;
-	for(int level = 0; level <= (level_runs ? max_level : 0); ++level)
+	const bool level_runs = sc.has_specular >= 2;
+	for(int level = 0; level <= (tree ? (1 << 20) : (level_runs ? max_level : 0)); ++level)     // tree mode: runs, until no tree ray is left
 	{
 	q_hit0.clear(); q_shadow.clear();
 	if(level == 0) for(uint32_t i = 0; i < n; ++i) primary(i, 0);
@@ -260,7 +266,12 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		}
 	}
 	W.ray = ray_buf[0];
-	if(level_runs && level < max_level)
+	if(tree)
+	{
+		for(uint32_t i : q_hit0) if(y4_stage_finish3(sc, W, ps, i) & Y4_PUSH_SPEC) q_spec_next.push_back(i);
+		if(q_spec_next.empty()) break;
+	}
+	else if(level_runs && level < max_level)
 		for(uint32_t i : q_hit0) if(y4_stage_level_finish(sc, W, ps, i, level) & Y4_PUSH_SPEC) q_spec_next.push_back(i);
 	}   // ray levels
 	for(uint32_t i = 0; i < n; ++i) y4_pt_finish_splat(sc, W, ps, i, film_w, film_rgba);

@@ -9,6 +9,7 @@ UNMODIFIED reference (oracle/_ref), committed so that the GPU box can check them
                        >= 200 000 instanced triangles at 240 x 135, 8 bounces + NEE, reference PathIntegrator in the deterministic
                        mode (threads = 1, linear tiles, RR off)
 
+  pt_glass.npz      <- Cornell box with `glass` objects (PT_GOLDEN_GLASS): reference PathIntegrator / DirectLightIntegrator, deterministic mode
   pt_rr.npz         <- Cornell box with the integrator's default Russian roulette (russian_roulette_min_bounces = 0), 1024 spp
 
 Run from the repo root:  python tests/golden/make_golden_large.py [soup|city]
@@ -60,6 +61,32 @@ def make_city():
     np.savez_compressed(os.path.join(HERE, "pt_city_large.npz"), **out)
 
 
+# glass: reflection + refraction at every vertex -> recursiveRaytrace is a tree (integrator_montecarlo.cc:918-968) -> pt_glass.npz
+PT_GOLDEN_GLASS = {
+    "glass_sphere": dict(width=96, height=54, spp=4, bounces=4, smooth_sphere=30.0, glass={"objects": ("sphere",), "IOR": 1.5}),
+    "glass_box_tinted": dict(width=96, height=54, spp=3, bounces=4, box_lift=0.013, glass={"objects": ("tall",), "IOR": 1.6, "filter_color": (0.4, 0.9, 0.6), "transmit_filter": 0.8,
+                                                                                 "mirror_color": (0.9, 0.8, 1.0)}),
+    "glass_and_mirror": dict(width=80, height=45, spp=3, bounces=3, smooth_sphere=30.0, box_lift=0.013, glass={"objects": ("sphere", "short"), "IOR": 1.6, "transmit_filter": 0.5, "filter_color": (1.0, 0.7, 0.5)},
+                             mirror={"objects": ("back",), "color": (0.9, 0.9, 0.9)}, integrator_extra={"raydepth": 4}),
+    "glass_direct_point": dict(width=80, height=45, spp=2, bounces=3, integrator="directlighting", point_light=True, smooth_sphere=30.0, box_lift=0.013, glass={"objects": ("sphere", "tall"), "IOR": 1.45}),
+    "glass_no_caustics_gauss": dict(width=80, height=45, spp=3, bounces=5, filter_type="gauss", smooth_sphere=30.0, glass={"objects": ("sphere",), "IOR": 1.5, "mirror_color": (0.5, 0.5, 0.5)},
+                                    integrator_extra={"caustic_type": "none", "raydepth": 3}),
+    "glass_deep_tree": dict(width=64, height=36, spp=2, bounces=5, box_lift=0.013, glass={"objects": ("tall", "short"), "IOR": 1.7, "transmit_filter": 0.7, "filter_color": (0.5, 0.8, 1.0)},
+                            integrator_extra={"raydepth": 6}),
+}
+
+
+def make_glass():
+    out = {}
+    for key, kw in PT_GOLDEN_GLASS.items():
+        t0 = time.time()
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print("%s: %.1f s" % (key, time.time() - t0), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_glass.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -80,6 +107,8 @@ if __name__ == "__main__":
         make_city()
     if "soup" in what:
         make_soup()
+    if "glass" in what:
+        make_glass()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

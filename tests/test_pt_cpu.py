@@ -47,6 +47,28 @@ def test_stages_vs_golden_reference_render(key):
     assert np.abs(img[..., 3] - ref[..., 3]).max() <= 1e-6
 
 
+def _glass_cfgs():
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_GLASS
+    return PT_GOLDEN_GLASS
+
+
+@pytest.mark.parametrize("key", ["glass_sphere", "glass_box_tinted", "glass_and_mirror", "glass_direct_point", "glass_no_caustics_gauss", "glass_deep_tree"])
+def test_glass_ray_tree_vs_golden_reference_render(key):
+    """`glass` (reflection AND refraction at a vertex: recursiveRaytrace is a tree) against the reference renders of
+    tests/golden/make_golden_large.py.  The tree is walked depth first and its branches are summed in walk order, the reference
+    sums from the leaves up: a few ulp per level.  (Glass boxes are lifted off the floor: a bottom face coinciding with the floor
+    gives exact ties in t, the documented class in which the kd-tree's leaf order decides.)"""
+    ref = np.load(os.path.join(GOLD, "pt_glass.npz"))[key]
+    a = _assemble(**_glass_cfgs()[key])
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 @pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
 def test_stages_vs_live_reference_multi_pass_and_rr():
     # multi-pass AA switches the pixel jitter to riVdC/riS; Russian roulette is statistical only (the reference draws
@@ -113,9 +135,14 @@ def test_transparent_shadow_mode_vs_live_reference():
 
 def test_interface_rejects_unsupported_features():
     yi = interface.Interface()
-    yi.paramsSetString("type", "glass")
+    yi.paramsSetString("type", "glossy")
     with pytest.raises(Y4Error):
         yi.createMaterial("g")
+    yi.paramsClearAll()
+    yi.paramsSetString("type", "glass")
+    yi.paramsSetFloat("dispersion_power", 0.1)          # chromatic dispersion: a spectral ray per wavelength
+    with pytest.raises(Y4Error):
+        yi.createMaterial("g2")
     yi.paramsClearAll()
     yi.paramsSetString("type", "shinydiffusemat")
     yi.paramsSetFloat("transparency", 0.5)
