@@ -239,7 +239,11 @@ typedef struct y4gpu_pt_layer     /* one `layer` node together with the `texture
    spherelight (light_sphere.cc; light sampling only, like the reference: canIntersect() is false),
    spotlight without soft_shadows (light_spot.cc: a dirac light with a smoothstep cone) */
 enum { Y4GPU_LIGHT_POINT = 0, Y4GPU_LIGHT_AREA = 1, Y4GPU_LIGHT_DIRECTIONAL = 2, Y4GPU_LIGHT_SUN = 3, Y4GPU_LIGHT_SPHERE = 4, Y4GPU_LIGHT_SPOT = 5,
-       Y4GPU_LIGHT_OBJECT = 6 };   /* `objectlight` / `meshlight` (light_object_light.cc): the triangles of a mesh emit */
+       Y4GPU_LIGHT_OBJECT = 6,     /* `objectlight` / `meshlight` (light_object_light.cc): the triangles of a mesh emit */
+       Y4GPU_LIGHT_BACKGROUND = 7 };   /* `bglight` (light_background.cc): the IBL light a `constant` / `gradientback` background creates with
+                                      ibl = true; it importance-samples the background of y4gpu_pt_params (tabulated on 360 latitude rows).
+                                      samples = `ibl_samples`, cast_shadows, double_sided = `abs_intersect`; put it where its name
+                                      ("constantBackground_bgLight" / "GradientBackground_bgLight") sorts among the lights */
 typedef struct y4gpu_pt_light
 {
 	int32_t type;                 /* Y4GPU_LIGHT_* ; lights in the reference's (name-sorted) order */

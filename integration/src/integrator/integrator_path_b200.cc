@@ -329,6 +329,7 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 		// ---- lights: the view's enabled lights in name order (render_view.cc:83-91) ----------------------------------------------------
 		std::vector<y4gpu_pt_light> lights;
 		std::vector<std::vector<float>> light_tris;
+		std::vector<std::string> ibl_light_names;
 		for(const auto &kv : render_view->getLights())
 		{
 			const Light *light = kv.second;
@@ -384,18 +385,27 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 				l.type = Y4GPU_LIGHT_OBJECT; l.samples = get<int>(p, "samples", 4); l.double_sided = get<bool>(p, "double_sided", false);
 				l.object_n_tris = (uint32_t) (tv.size() / 9);
 			}
+			else if(type == "bglight")      // created by a background's factory with ibl = true (background_constant.cc:58-69); checked against the rendered background below
+			{
+				l.type = Y4GPU_LIGHT_BACKGROUND; l.samples = get<int>(p, "samples", 16); l.double_sided = get<bool>(p, "abs_intersect", false);
+				ibl_light_names.push_back(kv.first);
+			}
 			else unsupported("light type '" + type + "'");
 			lights.push_back(l);
 		}
 		for(size_t i = 0, k = 0; i < lights.size(); ++i) if(lights[i].type == Y4GPU_LIGHT_OBJECT) lights[i].object_tris = light_tris[k++].data();
 		// ---- background ----------------------------------------------------------------------------------------------------------
+		bool rendered_background_has_ibl = false;
+		std::string ibl_light_name;
 		if(background_)
 		{
 			const ParamMap *bp = nullptr;
 			for(const auto &kv : rec.backgrounds) if(scene.getBackground(kv.first) == background_) bp = &kv.second;
 			if(!bp) unsupported("background without recorded parameters");
 			const std::string btype = getStr(*bp, "type");
-			if((btype != "constant" && btype != "gradientback") || get<bool>(*bp, "ibl", false)) unsupported("backgrounds other than constant / gradientback without IBL");
+			if(btype != "constant" && btype != "gradientback") unsupported("backgrounds other than constant / gradientback");
+			rendered_background_has_ibl = get<bool>(*bp, "ibl", false);
+			ibl_light_name = btype == "constant" ? "constantBackground_bgLight" : "GradientBackground_bgLight";
 			const float pw = get<float>(*bp, "power", 1.f);
 			const Rgb c = getCol(*bp, "color", Rgb{0.f});
 			pr.background[0] = c.r_ * pw; pr.background[1] = c.g_ * pw; pr.background[2] = c.b_ * pw;
@@ -408,6 +418,9 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 				for(int j = 0; j < 4; ++j) { pr.bg_gradient[j][0] = cols[j].r_ * pw; pr.bg_gradient[j][1] = cols[j].g_ * pw; pr.bg_gradient[j][2] = cols[j].b_ * pw; }
 			}
 		}
+		// an IBL light samples the background that created it: supported when that is the rendered background
+		for(const std::string &name : ibl_light_names)
+			if(!rendered_background_has_ibl || name != ibl_light_name) unsupported("IBL light '" + name + "' of a background other than the rendered one");
 		if(!get<bool>(rp, "background_resampling", true)) unsupported("background_resampling = false");
 		// ---- render parameters (scene.cc:528-644, imagefilm.cc:45-127) ---------------------------------------------------------------
 		pr.width = get<int>(rp, "width", cam.resx); pr.height = get<int>(rp, "height", cam.resy);

@@ -533,7 +533,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		if(mats[i].layer_count < 0 || (mats[i].layer_count > 0 && (mats[i].layer_first < 0 || !ctx->pt || (uint32_t) (mats[i].layer_first + mats[i].layer_count) > ctx->pt->n_layers)))
 		{ ctx->err = "material refers to layers that were not set (call y4gpu_pt_set_textures first)"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_light; ++i)
-		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_OBJECT) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
+		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_BACKGROUND) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	if(!ctx->pt) ctx->pt = new Y4Pt;
 	if(const char *e = getenv("Y4GPU_PT_MIN_BLOCKS")) ctx->pt->stage_min_blocks = atoi(e);
@@ -579,7 +579,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		chain_mats = chain_mats || mats[m].type == Y4GPU_MAT_MIRROR || mats[m].type == Y4GPU_MAT_GLASS || (mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f));
 	if(chain_mats && sc.no_recursive) { ctx->err = "no_recursive with mirror materials / specular_reflect is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 	// object lights need the general kernel variant as well (not the ray levels)
-	for(uint32_t l = 0; l < n_light; ++l) if(lights[l].type == Y4GPU_LIGHT_OBJECT && !sc.has_specular) sc.has_specular = 1;
+	for(uint32_t l = 0; l < n_light; ++l) if((lights[l].type == Y4GPU_LIGHT_OBJECT || lights[l].type == Y4GPU_LIGHT_BACKGROUND) && !sc.has_specular) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
@@ -614,6 +614,25 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 			pt->h_lights[i].obj_ng = reinterpret_cast<const float4 *>(blob);
 			pt->h_lights[i].obj_tris = reinterpret_cast<const float *>(blob + (size_t) n * 16);
 			pt->h_lights[i].obj_cdf = reinterpret_cast<const float *>(blob + (size_t) n * 52);
+		}
+		if(lights[i].type == Y4GPU_LIGHT_BACKGROUND)
+		{
+			// the tabulated background (BackgroundLight::init) in one device block: row offsets, function values, cdfs, 1 / integrals
+			std::vector<int> off; std::vector<float> func, cdf, inv_int;
+			derive_background_light(pt->h_lights[i], lights[i], *params, off, func, cdf, inv_int);
+			const size_t b_off = off.size() * 4, b_f = func.size() * 4, b_i = inv_int.size() * 4;
+			char *blob = nullptr;
+			Y4_CUDA(ctx, cudaMalloc(&blob, b_off + 2 * b_f + b_i));
+			pt->light_blobs.push_back(blob);
+			Y4_CUDA(ctx, cudaMemcpyAsync(blob, off.data(), b_off, cudaMemcpyHostToDevice, st));
+			Y4_CUDA(ctx, cudaMemcpyAsync(blob + b_off, func.data(), b_f, cudaMemcpyHostToDevice, st));
+			Y4_CUDA(ctx, cudaMemcpyAsync(blob + b_off + b_f, cdf.data(), b_f, cudaMemcpyHostToDevice, st));
+			Y4_CUDA(ctx, cudaMemcpyAsync(blob + b_off + 2 * b_f, inv_int.data(), b_i, cudaMemcpyHostToDevice, st));
+			Y4_CUDA(ctx, cudaStreamSynchronize(st));
+			pt->h_lights[i].bg_off = reinterpret_cast<const int *>(blob);
+			pt->h_lights[i].bg_func = reinterpret_cast<const float *>(blob + b_off);
+			pt->h_lights[i].bg_cdf = reinterpret_cast<const float *>(blob + b_off + b_f);
+			pt->h_lights[i].bg_inv_int = reinterpret_cast<const float *>(blob + b_off + 2 * b_f);
 		}
 		const int ns = y4_light_num_samples(sc, pt->h_lights[i]);
 		if(ns > pt->max_light_samples) pt->max_light_samples = ns;

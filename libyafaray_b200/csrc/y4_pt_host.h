@@ -192,7 +192,7 @@ inline Y4PtLight derive_light(const y4gpu_pt_light &l)
 	o.type = l.type; o.samples = l.samples; o.cast_shadows = l.cast_shadows;
 	o.pos = v3(l.from[0], l.from[1], l.from[2]);
 	o.color = c3(l.power * l.color[0], l.power * l.color[1], l.power * l.color[2]);       // color_ = col * inte
-	if(l.type == Y4GPU_LIGHT_POINT) return o;
+	if(l.type == Y4GPU_LIGHT_POINT || l.type == Y4GPU_LIGHT_BACKGROUND) return o;      // background light: derive_background_light
 	if(l.type == Y4GPU_LIGHT_DIRECTIONAL)                 // DirectionalLight ctor (light_directional.cc:28-39); init() only feeds photon code
 	{
 		o.dir = tov(normalized(hv(l.point1)));
@@ -280,6 +280,58 @@ inline void derive_object_light(Y4PtLight &o, const float *tris, uint32_t n, std
 	for(uint32_t i = 0; i < n; ++i) cdf[i] /= integral;
 	o.area = (float) total_area;
 	o.inv_area = (float) (1.f / total_area);
+}
+
+// Pdf1D::init / cumulateStep1DDf (sample_pdf1d.h:60-81): cdf of `n` function values appended to `cdf`; returns the integral
+inline float derive_pdf1d(const float *func, int n, std::vector<float> &cdf)
+{
+	const size_t at = cdf.size();
+	cdf.resize(at + n);
+	const double delta = 1.0 / (double) n;
+	double c = 0.0;
+	for(int i = 0; i < n; ++i) { c += (double) func[i] * delta; cdf[at + i] = (float) c; }
+	const float integral = (float) c;
+	for(int i = 0; i < n; ++i) cdf[at + i] /= integral;
+	return integral;
+}
+
+// BackgroundLight::init (light_background.cc:46-75): the background's energy * sin(theta) on 360 latitude rows of
+// 16 + (int)(sin(theta) * 704) columns, a Pdf1D per row and one over the row integrals.  The caller stores the arrays
+// where the light's pointers can reach them; the background's own description is copied into the light for eval().
+inline void derive_background_light(Y4PtLight &o, const y4gpu_pt_light &l, const y4gpu_pt_params &p,
+                                    std::vector<int> &off, std::vector<float> &func, std::vector<float> &cdf, std::vector<float> &inv_int)
+{
+	o.bg_abs_inter = l.double_sided;
+	o.bg_gradient = p.background_gradient;
+	o.bg_col = c3(p.background[0], p.background[1], p.background[2]);
+	o.bg_gz = c3(p.bg_gradient[0][0], p.bg_gradient[0][1], p.bg_gradient[0][2]); o.bg_gh = c3(p.bg_gradient[1][0], p.bg_gradient[1][1], p.bg_gradient[1][2]);
+	o.bg_sz = c3(p.bg_gradient[2][0], p.bg_gradient[2][1], p.bg_gradient[2][2]); o.bg_sh = c3(p.bg_gradient[3][0], p.bg_gradient[3][1], p.bg_gradient[3][2]);
+	const int nv = 360, max_u = 720, min_u = 16;
+	o.bg_nv = nv;
+	off.clear(); func.clear(); cdf.clear(); inv_int.clear();
+	std::vector<float> fv(nv);
+	const float inv_nv = 1.f / (float) nv;
+	for(int y = 0; y < nv; ++y)
+	{
+		const float fy = ((float) y + 0.5f) * inv_nv;
+		const float sintheta = y4_bg_sin_sample(fy);
+		const int nu = min_u + (int) (sintheta * (float) (max_u - min_u));
+		const float inv_nu = 1.f / (float) nu;
+		off.push_back((int) func.size());
+		for(int x = 0; x < nu; ++x)
+		{
+			const float fx = ((float) x + 0.5f) * inv_nu;
+			const C3 c = y4_bg_eval(o, y4_inv_sphere_map(fx, fy));
+			func.push_back(((c.r + c.g + c.b) * 0.333333f) * sintheta);            // Rgb::energy()
+		}
+		const float integral = derive_pdf1d(func.data() + off[y], nu, cdf);
+		fv[y] = integral;
+		inv_int.push_back(1.f / integral);
+	}
+	off.push_back((int) func.size());
+	func.insert(func.end(), fv.begin(), fv.end());
+	inv_int.push_back(1.f / derive_pdf1d(fv.data(), nv, cdf));
+	off.push_back((int) func.size());
 }
 
 // ImageFilm ctor: filter table, filter width, table scale (imagefilm.cc:129-173, math/filter.h:34-90)

@@ -413,6 +413,88 @@ Y4_HD bool y4_light_illuminate(const Y4PtLight &L, const V3 p, Y4LSample &ls)
 	return true;
 }
 
+// ---- background light (src/light/light_background.cc) ------------------------------------------------------------
+// ConstantBackground::eval / GradientBackground::eval (background_gradient.cc:34-46)
+Y4_HD C3 y4_bg_eval(const Y4PtLight &L, const V3 dir)
+{
+	if(!L.bg_gradient) return L.bg_col;
+	float blend = dir.z;
+	C3 color;
+	if(blend >= 0.f) color = cadd(cscale(L.bg_sz, blend), cscale(L.bg_sh, xsub(1.f, blend)));
+	else
+	{
+		blend = -blend;
+		color = cadd(cscale(L.bg_gz, blend), cscale(L.bg_gh, xsub(1.f, blend)));
+	}
+	if(fminf(color.r, fminf(color.g, color.b)) < 1e-6f) color = c3f(1e-5f);
+	return color;
+}
+// Pdf1D::sample (include/sampler/sample_pdf1d.h:99-122); lower_bound = first index with cdf[index] >= u
+Y4_HD float y4_pdf1d_sample(const float *func, const float *cdf, int n, float inv_integral, float u, float &pdf)
+{
+	if(u <= 0.f) { pdf = xmul(func[0], inv_integral); return 0.f; }
+	if(u >= 1.f) { pdf = xmul(func[n - 1], inv_integral); return xadd((float) (n - 1), 1.f); }
+	int lo = 0, hi = n;
+	while(lo < hi) { const int mid = (lo + hi) >> 1; if(cdf[mid] < u) lo = mid + 1; else hi = mid; }
+	const int index = lo < n ? lo : n - 1;      // (u above the last cdf entry would index past the table in the reference)
+	pdf = xmul(func[index], inv_integral);
+	const float delta = index > 0 ? xdiv(xsub(u, cdf[index - 1]), xsub(cdf[index], cdf[index - 1])) : xdiv(u, cdf[index]);
+	return xadd((float) index, delta);
+}
+Y4_HD float y4_bg_sin_sample(float s) { return y4_fast_sin((float) xdmul((Y4_WIDE) s, Y4_PI)); }      // math::sin(s * math::num_pi)
+Y4_HD float y4_bg_clamp_zero(float v) { return v > 0.f ? xdiv(1.f, v) : 0.f; }
+Y4_HD int y4_bg_clamp_sample(float v, int m) { int s = (int) xadd(v, 0.4999f); if(s > m - 1) s = m - 1; return s < 0 ? 0 : s; }     // clampSample(addOff(v), m)
+Y4_HD float y4_bg_pdf(float p0, float p1, float s, bool inv)
+{
+	if(inv) return fmaxf(0.000001f, xmul(xmul((float) Y4_2PI, y4_bg_sin_sample(s)), y4_bg_clamp_zero(xmul(p0, p1))));
+	return fmaxf(0.000001f, xmul(xmul(xmul(p0, p1), (float) Y4_1_2PI), y4_bg_clamp_zero(y4_bg_sin_sample(s))));
+}
+// Texture::invSphereMap / sphereMap (src/texture/texture.cc:103-132); acos is libm's on the host
+Y4_HD V3 y4_inv_sphere_map(float u, float v)
+{
+	const float theta = (float) xdmul((Y4_WIDE) v, Y4_PI), phi = -(float) xdmul((Y4_WIDE) u, Y4_2PI);
+	const float costheta = y4_fast_cos(theta), sintheta = y4_fast_sin(theta), cosphi = y4_fast_cos(phi), sinphi = y4_fast_sin(phi);
+	return v3(xmul(sintheta, cosphi), xmul(sintheta, sinphi), -costheta);
+}
+Y4_HD float y4_acos(float x) { return x <= -1.f ? (float) Y4_PI : (x >= 1.f ? 0.f : acosf(x)); }                     // math::acos
+Y4_HD void y4_sphere_map(const V3 p, float &u, float &v)
+{
+	const float sqrt_r_phi = xadd(xmul(p.x, p.x), xmul(p.y, p.y));
+	const float sqrt_r_theta = xadd(sqrt_r_phi, xmul(p.z, p.z));
+	u = 0.f;
+	if(sqrt_r_phi > 0.f)
+	{
+		const float a = y4_acos(xdiv(p.x, xsqrt(sqrt_r_phi)));
+		const float phi_ratio = p.y < 0.f ? (float) xdmul(Y4_2PI - (Y4_WIDE) a, Y4_1_2PI) : (float) xdmul((Y4_WIDE) a, Y4_1_2PI);
+		u = xsub(1.f, phi_ratio);
+	}
+	v = (float) (1.0 - xdmul((Y4_WIDE) y4_acos(xdiv(p.z, xsqrt(sqrt_r_theta))), Y4_1_PI));
+}
+// BackgroundLight::calcFromSample / calcFromDir (:77-101)
+Y4_HD float y4_bg_from_sample(const Y4PtLight &L, float s1, float s2, float &u, float &v, bool inv)
+{
+	float pdf1 = 0.f, pdf2 = 0.f;
+	const int nv = L.bg_nv, ov = L.bg_off[nv];
+	v = y4_pdf1d_sample(L.bg_func + ov, L.bg_cdf + ov, nv, L.bg_inv_int[nv], s2, pdf2);
+	const int iv = y4_bg_clamp_sample(v, nv);
+	const int ou = L.bg_off[iv], nu = L.bg_off[iv + 1] - ou;
+	u = y4_pdf1d_sample(L.bg_func + ou, L.bg_cdf + ou, nu, L.bg_inv_int[iv], s1, pdf1);
+	u = xmul(u, xdiv(1.f, (float) nu));
+	v = xmul(v, xdiv(1.f, (float) nv));
+	return y4_bg_pdf(pdf1, pdf2, v, inv);
+}
+Y4_HD float y4_bg_from_dir(const Y4PtLight &L, const V3 dir, float &u, float &v, bool inv)
+{
+	y4_sphere_map(dir, u, v);
+	const int nv = L.bg_nv;
+	const int iv = y4_bg_clamp_sample(xmul(v, (float) nv), nv);
+	const int ou = L.bg_off[iv], nu = L.bg_off[iv + 1] - ou;
+	const int iu = y4_bg_clamp_sample(xmul(u, (float) nu), nu);
+	const float pdf1 = xmul(L.bg_func[ou + iu], L.bg_inv_int[iv]);
+	const float pdf2 = xmul(L.bg_func[L.bg_off[nv] + iv], L.bg_inv_int[nv]);
+	return y4_bg_pdf(pdf1, pdf2, v, inv);
+}
+
 // Light::illumSample of the sampled lights: AreaLight (light_area.cc:66-96), SunLight (light_sun.cc:54-68),
 // SphereLight (light_sphere.cc:69-98)
 // GENERAL = false: the kernel variant for scenes without specular materials and object lights (see y4_vertex); the object
@@ -475,6 +557,15 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 		ls.dir = ldir; ls.tmax = dist; ls.col = L.color;
 		return true;
 	}
+	if(GENERAL && L.type == Y4GPU_LIGHT_BACKGROUND)       // BackgroundLight::illumSample (:127-137)
+	{
+		float u, v;
+		ls.pdf = y4_bg_from_sample(L, s1, s2, u, v, false);
+		ls.dir = y4_inv_sphere_map(u, v);
+		ls.col = y4_bg_eval(L, ls.dir);
+		ls.tmax = -1.f;
+		return true;
+	}
 	if(L.type == Y4GPU_LIGHT_SUN)
 	{
 		ls.dir = y4_sample_cone(L.dir, L.du, L.dv, L.cos_angle, s1, s2);
@@ -528,6 +619,14 @@ Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, f
 		}
 		ipdf = (float) xdmul((Y4_WIDE) xmul(xmul(1.f, L.area), cos_angle), Y4_1_PI);
 		col = L.color; t = -1.f;
+		return true;
+	}
+	if(GENERAL && L.type == Y4GPU_LIGHT_BACKGROUND)       // BackgroundLight::intersect (:139-151); `t` stays the caller's -1: unbounded shadow ray
+	{
+		float u, v;
+		ipdf = y4_bg_from_dir(L, L.bg_abs_inter ? xneg(dir) : dir, u, v, true);
+		col = y4_bg_eval(L, y4_inv_sphere_map(u, v));
+		t = -1.f;
 		return true;
 	}
 	if(L.type == Y4GPU_LIGHT_SUN)

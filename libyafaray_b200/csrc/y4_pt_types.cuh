@@ -100,10 +100,16 @@ struct Y4PtLight
 	const float *obj_tris;      // [obj_n * 9] world-space vertices
 	const float4 *obj_ng;       // [obj_n] Primitive::getGeometricNormal
 	const float *obj_cdf;       // [obj_n] Pdf1D::cdf_ of the triangle areas
+	// background light (light_background.cc:46-75): the background tabulated on bg_nv latitude rows of bg_off[y + 1] - bg_off[y]
+	// columns; row bg_nv of the tables is the distribution over the rows.  func = Pdf1D::function_, cdf = Pdf1D::cdf_.
+	int bg_nv, bg_abs_inter;
+	const int *bg_off;          // [bg_nv + 2]
+	const float *bg_func, *bg_cdf, *bg_inv_int;     // bg_inv_int[y] = Pdf1D::invIntegral() of row y
+	int bg_gradient; C3 bg_col, bg_gz, bg_gh, bg_sz, bg_sh;     // the background itself (Background::eval)
 };
 // Light::diracLight() / Light::canIntersect() of the supported lights (include/light/light_*.h)
 Y4_HD bool y4_light_dirac(int type) { return type == Y4GPU_LIGHT_POINT || type == Y4GPU_LIGHT_DIRECTIONAL || type == Y4GPU_LIGHT_SPOT; }
-Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN || type == Y4GPU_LIGHT_OBJECT; }
+Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN || type == Y4GPU_LIGHT_OBJECT || type == Y4GPU_LIGHT_BACKGROUND; }
 
 #define Y4_PT_MAX_LIGHTS 64
 #define Y4_FILTER_TABLE 16

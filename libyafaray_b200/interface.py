@@ -268,9 +268,16 @@ class Interface:
 
     def createBackground(self, name):
         p = dict(self.params)
-        if p.get("type") not in ("constant", "gradientback") or p.get("ibl", False):
-            raise Y4Error("only constant / gradientback backgrounds without IBL are supported by the GPU back end")
+        if p.get("type") not in ("constant", "gradientback"):
+            raise Y4Error("only constant / gradientback backgrounds are supported by the GPU back end")
         self.backgrounds[name] = p
+        if p.get("ibl", False):
+            # ConstantBackground::factory / GradientBackground::factory create the IBL light themselves, under a fixed name
+            # (background_constant.cc:58-69, background_gradient.cc:73-84); a second light of that name is refused by the scene
+            lname = "constantBackground_bgLight" if p["type"] == "constant" else "GradientBackground_bgLight"
+            if lname not in self.lights:
+                self.lights[lname] = dict(type="bglight", samples=int(p.get("ibl_samples", 16)), cast_shadows=bool(p.get("cast_shadows", True)),
+                                          _background=name)
         return True
 
     def createIntegrator(self, name):
@@ -601,6 +608,10 @@ class Interface:
                 self._light_tris.append(np.ascontiguousarray(ov))          # kept alive until the scene is uploaded
                 l.type, l.samples, l.double_sided = _lib.LIGHT_OBJECT, int(p.get("samples", 4)), int(p.get("double_sided", False))
                 l.object_n_tris, l.object_tris = len(ov), self._light_tris[-1].ctypes.data
+            elif p["type"] == "bglight":           # BackgroundLight::factory (light_background.cc:200-224); created by createBackground
+                if p["_background"] != rp.get("background_name", ""):
+                    raise Y4Error("an IBL light of a background other than the rendered one is not supported by the GPU back end")
+                l.type, l.samples, l.double_sided = _lib.LIGHT_BACKGROUND, int(p.get("samples", 16)), int(p.get("abs_intersect", False))
             elif p["type"] == "spherelight":       # SphereLight::factory (light_sphere.cc:160-195)
                 l.type, l.samples, l.radius = _lib.LIGHT_SPHERE, int(p.get("samples", 4)), float(p.get("radius", 1.0))
                 l.from_[:] = p.get("from", (0.0, 0.0, 0.0))

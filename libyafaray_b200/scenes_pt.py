@@ -84,11 +84,12 @@ def _uv_sphere(centre, radius, nu, nv):
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
                 oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None,
-                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None, mesh_light=None, glass=None, box_lift=0.0):
+                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None, mesh_light=None, glass=None, box_lift=0.0, lamp=True):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front.
     mirror: {"objects": subset of ("tall", "short", "back", "left", "sphere"), "color": rgb, "reflect": r} -> those objects get a
-    `mirror` material; integrator_extra: integrator parameters set after the defaults (raydepth, caustic_type, ...)."""
+    `mirror` material; integrator_extra: integrator parameters set after the defaults (raydepth, caustic_type, ...).
+    lamp=False: no ceiling lamp at all (the box is then lit through its open front, e.g. by a background with ibl=True)."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
     extra.update(shiny or {})          # shiny: shinydiffusemat parameters of all three wall materials (specular_reflect, mirror_color, fresnel_effect, IOR)
@@ -140,7 +141,7 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     _mesh(api, "g_short", mat("short", "white"), v, t)
     # emitting quad just below the ceiling, facing down; the area light shares its corners
     lx0, lx1, lz0, lz1, ly = 0.37, 0.63, 0.395, 0.605, 0.999
-    if not point_light:
+    if not point_light and lamp:
         v, t = _quad((lx0, ly, lz0), (lx1, ly, lz0), (lx1, ly, lz1), (lx0, ly, lz1))
         _mesh(api, "h_lamp", "emitter", v, t)
     if smooth_sphere is not None:       # a sphere on the short box, shaded with yafaray_smoothMesh(angle)
@@ -177,7 +178,8 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         api.paramsSetFloat("power", 18.0)
         api.paramsSetInt("samples", light_samples)
         api.paramsSetString("object_name", "h_lamp")
-    api.createLight("lamp")
+    if lamp:
+        api.createLight("lamp")
     for kind in extra_lights:
         api.paramsClearAll()
         if kind == "sun":                               # wide cone so that several samples differ visibly

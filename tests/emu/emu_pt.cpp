@@ -131,7 +131,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	}
 	if(sc.has_specular == 3 && params->transp_background) return -3;
 	// object lights need the general kernel variant as well (not the ray levels)
-	for(uint32_t l = 0; l < n_light; ++l) if(lights[l].type == Y4GPU_LIGHT_OBJECT && !sc.has_specular) sc.has_specular = 1;
+	for(uint32_t l = 0; l < n_light; ++l) if((lights[l].type == Y4GPU_LIGHT_OBJECT || lights[l].type == Y4GPU_LIGHT_BACKGROUND) && !sc.has_specular) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
@@ -151,7 +151,14 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 			obj_tris[i].assign(lights[i].object_tris, lights[i].object_tris + 9ull * lights[i].object_n_tris);
 			derive_object_light(hl[i], obj_tris[i].data(), lights[i].object_n_tris, obj_cdf[i], obj_ng[i]);
 			hl[i].obj_tris = obj_tris[i].data(); hl[i].obj_cdf = obj_cdf[i].data(); hl[i].obj_ng = obj_ng[i].data();
-		} const int ns = y4_light_num_samples(sc, hl[i]); if(ns > max_ls) max_ls = ns; }
+		}
+		if(lights[i].type == Y4GPU_LIGHT_BACKGROUND)
+		{
+			static std::vector<int> bg_off; static std::vector<float> bg_func, bg_cdf, bg_inv;     // (one background light per scene)
+			derive_background_light(hl[i], lights[i], *params, bg_off, bg_func, bg_cdf, bg_inv);
+			hl[i].bg_off = bg_off.data(); hl[i].bg_func = bg_func.data(); hl[i].bg_cdf = bg_cdf.data(); hl[i].bg_inv_int = bg_inv.data();
+		}
+		const int ns = y4_light_num_samples(sc, hl[i]); if(ns > max_ls) max_ls = ns; }
 	std::vector<float4> tri_shade(n_tri);
 	for(int t = 0; t < n_tri; ++t) tri_shade[t] = y4_tri_shade(verts, flags, n_mat, (uint64_t) t);
 	std::vector<Y4PtMaterial> hm(n_mat);

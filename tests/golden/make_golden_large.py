@@ -10,6 +10,7 @@ UNMODIFIED reference (oracle/_ref), committed so that the GPU box can check them
                        mode (threads = 1, linear tiles, RR off)
 
   pt_glass.npz      <- Cornell box with `glass` objects (PT_GOLDEN_GLASS): reference PathIntegrator / DirectLightIntegrator, deterministic mode
+  pt_ibl.npz        <- Cornell box lit by an IBL background light (PT_GOLDEN_IBL), deterministic mode
   pt_rr.npz         <- Cornell box with the integrator's default Russian roulette (russian_roulette_min_bounces = 0), 1024 spp
 
 Run from the repo root:  python tests/golden/make_golden_large.py [soup|city]
@@ -87,6 +88,32 @@ def make_glass():
     np.savez_compressed(os.path.join(HERE, "pt_glass.npz"), **out)
 
 
+# IBL: a `constant` / `gradientback` background with ibl=True creates a `bglight` that importance-samples it (light_background.cc) -> pt_ibl.npz
+_SKY = dict(type="gradientback", horizon_color=(1.0, 0.9, 0.7, 1.0), zenith_color=(0.2, 0.4, 1.0, 1.0), horizon_ground_color=(0.5, 0.4, 0.3, 1.0),
+            zenith_ground_color=(0.1, 0.1, 0.1, 1.0), power=2.0, ibl=True)
+PT_GOLDEN_IBL = {
+    "ibl_constant": dict(width=96, height=54, spp=3, bounces=4, lamp=False, background=dict(type="constant", color=(0.8, 0.9, 1.0, 1.0), power=1.5, ibl=True, ibl_samples=3)),
+    "ibl_gradient": dict(width=96, height=54, spp=4, bounces=5, lamp=False, smooth_sphere=30.0, background=dict(_SKY, ibl_samples=1)),
+    "ibl_gradient_mirror_gauss": dict(width=80, height=45, spp=3, bounces=4, lamp=False, filter_type="gauss", background=dict(_SKY, ibl_samples=2),
+                                      mirror={"objects": ("tall", "back"), "color": (0.9, 0.9, 0.9)}, integrator_extra={"caustic_type": "path"}),
+    "ibl_direct_with_lamp": dict(width=80, height=45, spp=2, bounces=3, integrator="directlighting", light_samples=2, background=dict(_SKY, ibl_samples=4)),
+    "ibl_no_shadows": dict(width=64, height=36, spp=2, bounces=3, lamp=False, background=dict(_SKY, ibl_samples=2, cast_shadows=False)),
+    # two lights under path tracing: the reference picks the light of a path vertex from a call counter (checked through the emulation only)
+    "ibl_path_with_lamp": dict(width=64, height=36, spp=3, bounces=4, background=dict(_SKY, ibl_samples=1)),
+}
+
+
+def make_ibl():
+    out = {}
+    for key, kw in PT_GOLDEN_IBL.items():
+        t0 = time.time()
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print("%s: %.1f s" % (key, time.time() - t0), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_ibl.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -109,6 +136,8 @@ if __name__ == "__main__":
         make_soup()
     if "glass" in what:
         make_glass()
+    if "ibl" in what:
+        make_ibl()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

@@ -69,6 +69,26 @@ def test_glass_ray_tree_vs_golden_reference_render(key):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+def _ibl_cfgs():
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_IBL
+    return PT_GOLDEN_IBL
+
+
+@pytest.mark.parametrize("key", ["ibl_constant", "ibl_gradient", "ibl_gradient_mirror_gauss", "ibl_direct_with_lamp", "ibl_no_shadows", "ibl_path_with_lamp"])
+def test_background_light_vs_golden_reference_render(key):
+    """A background with ibl=True: the `bglight` it creates (light_background.cc) tabulates the background on 360 latitude rows
+    and importance-samples it; sampled directions, pdfs and the MIS partner (BackgroundLight::intersect) are sample-exact."""
+    ref = np.load(os.path.join(GOLD, "pt_ibl.npz"))[key]
+    a = _assemble(**_ibl_cfgs()[key])
+    w, rgba = helpers.emu_pt_render(a, ref_light_order=a["n_light"] > 1 and a["params"].path_samples > 0)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 @pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
 def test_stages_vs_live_reference_multi_pass_and_rr():
     # multi-pass AA switches the pixel jitter to riVdC/riS; Russian roulette is statistical only (the reference draws
