@@ -80,6 +80,8 @@ typedef struct y4gpu_stats
 	uint64_t kernel_launches;           /* kernels launched by this ctx since creation */
 	uint64_t bvh_levels;                /* depth of the BVH8 of the last build (the traversal stack holds Y4_STACK_SIZE = 64 entries;
 	                                       builds deeper than 56 levels are refused with Y4GPU_ERR_UNSUPPORTED) */
+	uint64_t last_trace_sorted;         /* 1: the last resident y4gpu_trace batch was traced in sorted ray order (y4gpu_set_ray_sort) */
+	double last_probe_distinct;         /* automatic mode: distinct coarse ray keys per 32 consecutive rays found by the probe */
 } y4gpu_stats;
 
 /* lifetime ------------------------------------------------------------------------------ */
@@ -114,6 +116,14 @@ int y4gpu_get_bound(const y4gpu_ctx *ctx, float out_bound[6]);
  * H2D copy, traversal and D2H copy overlap on several streams (pass page-locked buffers, y4gpu_host_alloc, for that).
  * Device buffers: queued on the context's stream, not waited for; such calls are serialised by the context's mutex. */
 int y4gpu_trace(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out);
+/* Ray order of large batches (>= 65536 rays; y4gpu_trace closest / shadow).  A tuning knob without a counterpart in the
+ * reference.  mode 0: rays are traced in the order given.  1: every batch is traced in the order of a 32-bit key (Morton
+ * code of the origin's cell in the tree bound, then a direction class) through an index queue -- results are bit-identical,
+ * only the order in which warps pick rays up changes.  2 (default): sorted only when the BVH is much larger than L2
+ * (>= 256 MB) AND a probe of the batch (one small kernel + one synchronisation) finds it incoherent as laid out.
+ * Worth it where traversal is bound by DRAM sector fetches (50 M triangles, random rays); a loss on camera rays.
+ * Scratch (16 B per ray + the radix sort's temporary storage) is allocated on first use and kept. */
+int y4gpu_set_ray_sort(y4gpu_ctx *ctx, int mode);
 /* same, plus per-batch node/triangle visit counters in y4gpu_stats (slower; for the roofline) */
 int y4gpu_trace_counted(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out);
 /* transparent shadows: mat_transparency = n_mat * 3 floats (Material::getTransparency colour) */

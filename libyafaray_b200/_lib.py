@@ -34,6 +34,7 @@ class Stats(C.Structure):
         ("last_trace_rays", C.c_uint64),
         ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
         ("kernel_launches", C.c_uint64), ("bvh_levels", C.c_uint64),
+        ("last_trace_sorted", C.c_uint64), ("last_probe_distinct", C.c_double),
     ]  # fmt: skip
 
 
@@ -131,7 +132,7 @@ EXPORTED = [
     "y4gpu_set_stream", "y4gpu_host_alloc", "y4gpu_host_free",
     "y4gpu_upload_triangles", "y4gpu_build", "y4gpu_get_bound",
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow", "y4gpu_trace_tshadow_inner", "y4gpu_trace_noalloc",
-    "y4gpu_get_stats", "y4gpu_synchronize",
+    "y4gpu_set_ray_sort", "y4gpu_get_stats", "y4gpu_synchronize",
     "y4gpu_pt_set_textures", "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
     "y4gpu_pt_read_film", "y4gpu_pt_write_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass",
 ]  # fmt: skip
@@ -174,6 +175,8 @@ def lib() -> C.CDLL:
     L.y4gpu_trace_tshadow.restype = i32
     L.y4gpu_trace_tshadow_inner.argtypes = [vp, vp, u64, i32, vp, u32, vp]
     L.y4gpu_trace_tshadow_inner.restype = i32
+    L.y4gpu_set_ray_sort.argtypes = [vp, i32]
+    L.y4gpu_set_ray_sort.restype = i32
     L.y4gpu_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.y4gpu_get_stats.restype = i32
     L.y4gpu_synchronize.argtypes = [vp]

@@ -138,6 +138,11 @@ class AcceleratorB200:
         """Run this accelerator's kernels/copies on the caller's CUDA stream (0/None = its own)."""
         _lib.check(self._ctx, self._L.y4gpu_set_stream(self._ctx, C.c_void_p(int(cuda_stream or 0))), "y4gpu_set_stream")
 
+    def set_ray_sort(self, mode: int) -> None:
+        """Ray order of large batches: 0 as given, 1 always sorted by origin cell + direction class, 2 automatic (default).
+        Results are bit-identical in every mode (include/y4gpu.h: y4gpu_set_ray_sort)."""
+        _lib.check(self._ctx, self._L.y4gpu_set_ray_sort(self._ctx, int(mode)), "y4gpu_set_ray_sort")
+
     # -- diagnostics -------------------------------------------------------------------------
     def synchronize(self) -> None:
         _lib.check(self._ctx, self._L.y4gpu_synchronize(self._ctx), "y4gpu_synchronize")

@@ -5,6 +5,8 @@
 #include <cstdlib>
 
 static std::string g_create_err;
+extern "C" { static void ray_sort_env(y4gpu_ctx *ctx); }
+
 extern "C" { static void slot_free_all(y4gpu_ctx *ctx); }
 
 static bool is_device_ptr(const void *p)
@@ -61,6 +63,7 @@ int y4gpu_create(int device, y4gpu_ctx **out)
 	if(const char *e = getenv("Y4GPU_TREELET_DEFER")) { const int k = atoi(e); ctx->treelet_defer = k < 0 ? 0 : (k > 1024 ? 1024 : k); }
 	if(const char *e = getenv("Y4GPU_TREELET")) { const int k = atoi(e); ctx->treelet_leaves = k < 0 ? 0 : (k > 4096 ? 4096 : k); }
 	if(const char *e = getenv("Y4GPU_MIN_BLOCKS")) ctx->min_blocks = atoi(e);
+	ray_sort_env(ctx);
 	*out = ctx;
 	return Y4GPU_OK;
 }
@@ -77,7 +80,7 @@ void y4gpu_destroy(y4gpu_ctx *ctx)
 	slot_free_all(ctx);
 	cudaFree(ctx->d_verts); cudaFree(ctx->d_flags); cudaFree(ctx->d_nodes); cudaFree(ctx->d_tris);
 	cudaFree(ctx->d_rays); cudaFree(ctx->d_hits); cudaFree(ctx->d_work_counter); cudaFree(ctx->d_visit_counters); cudaFree(ctx->d_consts);
-	cudaFree(ctx->d_mat_transp);
+	cudaFree(ctx->d_mat_transp); cudaFree(ctx->sort_scratch.buf);
 	if(ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if(ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if(ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -205,6 +208,7 @@ static void slot_free_all(y4gpu_ctx *ctx)
 		if(s->ev1) cudaEventDestroy(s->ev1);
 		if(s->ev_dep) cudaEventDestroy(s->ev_dep);
 		cudaFree(s->d_rays); cudaFree(s->d_hits); cudaFree(s->d_counters); cudaFree(s->d_mat_transp);
+		for(int i = 0; i < Y4TraceSlot::kStreams; ++i) cudaFree(s->sort[i].buf);
 		if(s->h_pinned) cudaFreeHost(s->h_pinned);
 		delete s;
 	}
@@ -236,6 +240,16 @@ constexpr uint64_t kMinChunk = 1ull << 18;      // rays per pipelined chunk, at 
 // go round-robin over the slot's streams (H2D copy -> kernel -> D2H copy per chunk), so the copies of one chunk overlap the
 // traversal of another and both copy engines stay busy; the caller's buffers should be page-locked (y4gpu_host_alloc) for the
 // copies to be asynchronous.  tshadow: mat != null.
+// tuning knobs of the ray sort, read when a context is created and again by y4gpu_set_ray_sort
+static void ray_sort_env(y4gpu_ctx *ctx)
+{
+	if(const char *e = getenv("Y4GPU_RAY_SORT")) { const int k = atoi(e); ctx->ray_sort = k < 0 ? 0 : (k > 2 ? 2 : k); }
+	if(const char *e = getenv("Y4GPU_RAY_SORT_OBITS")) { const int k = atoi(e); ctx->ray_sort_obits = k < 1 ? 1 : (k > 8 ? 8 : k); }
+	if(const char *e = getenv("Y4GPU_RAY_SORT_DIR_MAJOR")) ctx->ray_sort_dir_major = atoi(e) != 0;
+	if(const char *e = getenv("Y4GPU_RAY_SORT_MIN_DISTINCT")) ctx->ray_sort_min_distinct = (float) atof(e);
+	if(const char *e = getenv("Y4GPU_RAY_SORT_MIN_BVH_MB")) ctx->ray_sort_min_bvh_bytes = (uint64_t) atoll(e) << 20;
+}
+
 static int trace_host(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, void *out, uint64_t hit_bytes,
                       int max_depth, const float *mat_transparency, uint32_t n_mat, bool inner)
 {
@@ -289,6 +303,11 @@ static int trace_host(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t 
 		h_stage = static_cast<char *>(s->h_pinned);
 		memcpy(h_stage, rays, n * sizeof(Y4Ray));
 	}
+	// sorted chunks (y4gpu_set_ray_sort): decided once per batch on its first chunk; every stream sorts in its own scratch
+	bool sorted = false;
+	const bool may_sort = !tshadow && ctx->ray_sort != 0 && chunk >= (1u << 16);
+	if(may_sort)
+		for(int i = 0; i < n_streams; ++i) { const int rc = y4_sort_scratch_reserve(ctx, s->sort[i], chunk); if(rc) return rc; }
 	for(uint64_t c = 0; c < n_chunks; ++c)
 	{
 		cudaStream_t st = s->streams[c % (uint64_t) n_streams];
@@ -296,7 +315,9 @@ static int trace_host(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t 
 		Y4_SLOT_CUDA(ctx, cudaMemcpyAsync(s->d_rays + first, small ? (const void *) h_stage : (const void *) (rays + first), cnt * sizeof(Y4Ray), cudaMemcpyHostToDevice, st));
 		char *d_hits = static_cast<char *>(s->d_hits) + first * hit_bytes;
 		int rc;
-		if(tshadow) rc = y4_launch_tshadow_on(ctx, s->d_rays + first, cnt, max_depth, s->d_mat_transp, n_mat, reinterpret_cast<y4gpu_tshit *>(d_hits), inner, s->d_counters + c, st);
+		if(may_sort && c == 0) { rc = y4_ray_sort_wanted(ctx, s->d_rays, cnt, s->sort[0], st, sorted); if(rc) return rc; }
+		if(sorted && cnt >= (1u << 16)) rc = y4_launch_trace_sorted(ctx, kind, s->d_rays + first, cnt, reinterpret_cast<Y4Hit *>(d_hits), s->d_counters + c, s->sort[c % (uint64_t) n_streams], st);
+		else if(tshadow) rc = y4_launch_tshadow_on(ctx, s->d_rays + first, cnt, max_depth, s->d_mat_transp, n_mat, reinterpret_cast<y4gpu_tshit *>(d_hits), inner, s->d_counters + c, st);
 		else rc = y4_launch_trace_on(ctx, kind, s->d_rays + first, cnt, reinterpret_cast<Y4Hit *>(d_hits), s->d_counters + c, st);
 		if(rc) return rc;
 		char *h_dst = small ? h_stage + n * sizeof(Y4Ray) : static_cast<char *>(out) + first * hit_bytes;
@@ -314,7 +335,8 @@ static int trace_host(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t 
 	cudaEventElapsedTime(&ms, s->ev0, s->ev1);
 	{
 		std::lock_guard<std::mutex> lk(ctx->stat_mtx);
-		ctx->stats.kernel_launches += n_chunks;
+		ctx->stats.kernel_launches += sorted ? 2 * n_chunks : n_chunks;
+		ctx->stats.last_trace_sorted = sorted ? 1 : 0;
 		ctx->stats.last_trace_rays = n;
 		ctx->stats.last_trace_ms = ms;          // copies included (the whole pipelined batch)
 		ctx->last_trace_async = false;
@@ -358,6 +380,17 @@ static int trace_impl(y4gpu_ctx *ctx, int kind, bool counted, const y4gpu_ray *r
 }
 
 int y4gpu_trace(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out) { return trace_impl(ctx, kind, false, rays, n, out); }
+
+int y4gpu_set_ray_sort(y4gpu_ctx *ctx, int mode)
+{
+	if(!ctx || mode < 0 || mode > 2) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	ctx->ray_sort = mode;
+	const int keep = ctx->ray_sort;
+	ray_sort_env(ctx);                 // the finer knobs (key bits, thresholds) follow the environment
+	ctx->ray_sort = keep;
+	return Y4GPU_OK;
+}
 int y4gpu_trace_counted(y4gpu_ctx *ctx, int kind, const y4gpu_ray *rays, uint64_t n, y4gpu_hit *out) { return trace_impl(ctx, kind, true, rays, n, out); }
 
 static int tshadow_impl(y4gpu_ctx *ctx, const y4gpu_ray *rays, uint64_t n, int max_depth, const float *mat_transparency, uint32_t n_mat, y4gpu_tshit *out, bool inner)
@@ -429,6 +462,7 @@ int y4gpu_get_stats(const y4gpu_ctx *ctx, y4gpu_stats *out)
 {
 	if(!ctx || !out) return Y4GPU_ERR_ARG;
 	*out = ctx->stats;
+	out->last_probe_distinct = ctx->last_probe_distinct;
 	float ms = 0.f;
 	// a batch queued on the context's stream is timed by its events once they have completed; the slot path stores its time directly
 	if(ctx->last_trace_async)

@@ -12,6 +12,9 @@ struct Y4Pt;   // wavefront path tracer state (y4_pt.cu)
 // Everything one host-buffer ray batch needs, so that concurrent callers (the Accelerator virtuals are called from every
 // render thread, integrator_tiled.cc:248-251) never share a stream, a staging buffer or a work counter.  Slots are pooled
 // per context; a call takes one off the free list (or creates it) and puts it back when its streams have drained.
+// device scratch of a sorted ray batch (y4_trace.cu: keys, indices, CUB temporary storage); grown on demand, never shrunk
+struct Y4SortScratch { void *buf = nullptr; size_t cap = 0; };
+
 struct Y4TraceSlot
 {
 	static constexpr int kStreams = 4, kMaxChunks = 64;
@@ -22,6 +25,7 @@ struct Y4TraceSlot
 	unsigned long long *d_counters = nullptr;        // kMaxChunks work counters
 	float *d_mat_transp = nullptr; uint32_t mat_transp_cap = 0;
 	void *h_pinned = nullptr; size_t pinned_bytes = 0;   // staging of small batches (1-ray calls): truly asynchronous copies
+	Y4SortScratch sort[kStreams];                        // sorted chunks: one scratch per stream
 };
 
 struct y4gpu_ctx
@@ -65,6 +69,14 @@ struct y4gpu_ctx
 	int treelet_defer = 64;    // sub-ranges of a treelet with at most this many leaves are split by a second, wider launch (env Y4GPU_TREELET_DEFER; 0 = one pass)
 	int treelet_leaves = 2048;  // SAH rebuild of the binary subtrees with at most this many leaves (0 = plain LBVH; env Y4GPU_TREELET, <= 4096)
 
+	// ray sorting (y4gpu_set_ray_sort; env Y4GPU_RAY_SORT / _OBITS / _DIR_MAJOR / _MIN_DISTINCT / _MIN_BVH_MB at creation)
+	int ray_sort = 2;                          // 0 never, 1 every batch of >= 65536 rays, 2 automatic (probe)
+	int ray_sort_obits = 6, ray_sort_dir_major = 0;
+	float ray_sort_min_distinct = 12.f;        // automatic mode: mean number of distinct coarse keys per 32 consecutive rays
+	uint64_t ray_sort_min_bvh_bytes = 256ull << 20;
+	float last_probe_distinct = 0.f;
+	Y4SortScratch sort_scratch;
+
 	y4gpu_stats stats = {};
 	bool last_trace_async = false;             // the last batch ran on the context's stream and is timed by ev0 / ev1
 	std::mutex stat_mtx;                       // guards `stats` updates of the slot path
@@ -95,6 +107,11 @@ int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_
 int y4_launch_tshadow_wave(y4gpu_ctx *ctx, const Y4Ray *d_rays, Y4Hit *d_out, const uint32_t *d_queue, const uint32_t *d_queue_count, int max_depth,
                            const float *d_mat_transp, uint32_t n_mat, unsigned long long *d_work_counter, cudaStream_t stream, int max_blocks_per_sm);
 int y4_launch_tshadow(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out);
+// ray sorting: decision (automatic mode probes the batch: one small kernel + a synchronisation of `stream`) and the sorted launch
+int y4_sort_scratch_reserve(y4gpu_ctx *ctx, Y4SortScratch &sc, uint64_t n);
+int y4_ray_sort_wanted(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, Y4SortScratch &sc, cudaStream_t stream, bool &want);
+int y4_launch_trace_sorted(y4gpu_ctx *ctx, int kind, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out, unsigned long long *d_work_counter,
+                           Y4SortScratch &sc, cudaStream_t stream);
 // launches on an explicit stream with an explicit (pre-zeroed) work counter: the re-entrant host-buffer path of y4_api.cu
 int y4_launch_trace_on(y4gpu_ctx *ctx, int kind, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out, unsigned long long *d_work_counter, cudaStream_t stream);
 int y4_launch_tshadow_on(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out,

@@ -96,14 +96,22 @@ struct StageQueues
 };
 
 __global__ void __launch_bounds__(kPtThreads) k_pt_gen(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, const uint32_t *__restrict__ pixel_list,
-                                                        uint64_t first, uint32_t ns_local, int shard_index, int shard_count)
+                                                        uint64_t first, uint64_t n_pix, uint32_t ns_local, int shard_index, int shard_count)
 {
+	// Enumeration of the pass's pixel-samples: blocks of 32 consecutive pixels, inside a block sample-major, so that the lanes of
+	// a warp hold the same sample index of 32 neighbouring pixels.  Their film updates then go to neighbouring addresses
+	// (one vector RED per lane over 512 contiguous bytes) instead of 16 lanes adding to the same pixel.
 	for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < W.n; i += gridDim.x * blockDim.x)
 	{
 		const uint64_t g = first + i;
-		const uint64_t slot = g / ns_local;
+		const uint64_t per_block = 32ull * ns_local;
+		const uint64_t blk = g / per_block;
+		const uint32_t r = (uint32_t) (g - blk * per_block);
+		const uint64_t left = n_pix - 32ull * blk;
+		const uint32_t in_blk = left < 32ull ? (uint32_t) left : 32u;
+		const uint64_t slot = 32ull * blk + r % in_blk;
 		W.pix[i] = pixel_list ? pixel_list[slot] : (uint32_t) slot;
-		W.samp[i] = (uint32_t) shard_index + (uint32_t) (g % ns_local) * (uint32_t) shard_count;
+		W.samp[i] = (uint32_t) shard_index + (r / in_blk) * (uint32_t) shard_count;
 		y4_pt_gen(sc, W, ps, i);
 	}
 }
@@ -1015,7 +1023,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 		if(level == 0)
 		{
 			// camera rays -> closest hits -> camera-hit stage with the first light sample
-			Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, ns_local, shard_index, shard_count));
+			Y4_PT_LAUNCH(0, k_pt_gen<<<grid, kPtThreads, 0, st>>>(dsc, W, ps, d_list, first, n_pix, ns_local, shard_index, shard_count));
 			Y4_PT_TRACE(Y4_TRACE_CLOSEST, W.ray, W.hit, W.n, nullptr, nullptr); pt->dense_closest += W.n;
 		}
 		else

@@ -6,6 +6,7 @@
 // (2 x float4 in, 1 x float4 out per ray); node and triangle fetches are 128-bit
 // read-only loads (y4_ld_u4 / y4_ld_tri).
 #include "y4_ctx.h"
+#include <cub/cub.cuh>
 
 namespace {
 
@@ -264,7 +265,133 @@ int launch(y4gpu_ctx *ctx, bool counted, const TraceArgs &a)
 	return ctx->min_blocks >= 4 ? launch_k<KIND, false, 4, QUEUE>(ctx, a) : launch_k<KIND, false, 3, QUEUE>(ctx, a);
 }
 
+// ---- ray sorting ---------------------------------------------------------------------------------------------------
+// Incoherent batches over a BVH much larger than L2 (C5: 50 M triangles, 3.6 GB) are bound by DRAM sector fetches: every
+// lane of a warp walks its own part of the tree.  Tracing the batch in the order of a 32-bit key -- the Morton code of the
+// ray origin's cell in the tree bound, then a 6-bit direction class -- puts rays that start close together and head the same
+// way into the same warps, so their node and triangle fetches hit the same lines.  Only the ORDER changes: k_trace runs over
+// an index queue (its QUEUE variant) and writes every hit to the ray's own slot, so results are bit-identical.
+__device__ __forceinline__ uint32_t y4_spread3(uint32_t v)        // 10 bits -> every third bit
+{
+	v = (v | (v << 16)) & 0x030000FFu;
+	v = (v | (v << 8)) & 0x0300F00Fu;
+	v = (v | (v << 4)) & 0x030C30C3u;
+	v = (v | (v << 2)) & 0x09249249u;
+	return v;
+}
+__device__ __forceinline__ uint32_t y4_ray_sort_key(const float4 a, const float4 b, float lx, float ly, float lz, float sx, float sy, float sz,
+                                                    int obits, int dir_major)
+{
+	const int top = (1 << obits) - 1;
+	const int cx = min(max((int) ((a.x - lx) * sx), 0), top), cy = min(max((int) ((a.y - ly) * sy), 0), top), cz = min(max((int) ((a.z - lz) * sz), 0), top);
+	const uint32_t m = y4_spread3((uint32_t) cx) | (y4_spread3((uint32_t) cy) << 1) | (y4_spread3((uint32_t) cz) << 2);
+	const float ax = fabsf(b.x), ay = fabsf(b.y), az = fabsf(b.z);
+	const uint32_t oct = (b.x < 0.f ? 4u : 0u) | (b.y < 0.f ? 2u : 0u) | (b.z < 0.f ? 1u : 0u);
+	const uint32_t dom = ax >= ay ? (ax >= az ? 0u : 2u) : (ay >= az ? 1u : 2u);
+	const float big = fmaxf(ax, fmaxf(ay, az)), mid = ax + ay + az - big - fminf(ax, fminf(ay, az));
+	const uint32_t d = (oct << 3) | (dom << 1) | (mid >= 0.5f * big ? 1u : 0u);
+	return dir_major ? ((d << (3 * obits)) | m) : ((m << 6) | d);
+}
+__global__ void __launch_bounds__(256) k_ray_sort_keys(const Y4Ray *__restrict__ rays, uint32_t n, float lx, float ly, float lz, float sx, float sy, float sz,
+                                                       int obits, int dir_major, uint32_t *__restrict__ keys, uint32_t *__restrict__ idx, uint32_t *__restrict__ count)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i == 0) *count = n;
+	if(i >= n) return;
+	const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + i)), b = __ldg(reinterpret_cast<const float4 *>(rays + i) + 1);
+	keys[i] = y4_ray_sort_key(a, b, lx, ly, lz, sx, sy, sz, obits, dir_major);
+	idx[i] = i;
+}
+// Coherence probe of the automatic mode: over every 64th group of 32 consecutive rays, the number of distinct coarse keys
+// (4 bits per axis + direction class) in the group.  Camera rays give 1-3, uniformly random rays 32.
+__global__ void __launch_bounds__(256) k_ray_sort_probe(const Y4Ray *__restrict__ rays, uint32_t n_groups, uint32_t group_stride, float lx, float ly, float lz,
+                                                        float sx, float sy, float sz, unsigned long long *__restrict__ distinct_sum)
+{
+	const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+	if(warp >= n_groups) return;
+	const uint64_t i = (uint64_t) warp * group_stride * 32ull + lane;
+	const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + i)), b = __ldg(reinterpret_cast<const float4 *>(rays + i) + 1);
+	const uint32_t key = y4_ray_sort_key(a, b, lx, ly, lz, sx, sy, sz, 4, 0);
+	const uint32_t same = __match_any_sync(0xffffffffu, key);
+	const uint32_t leaders = __ballot_sync(0xffffffffu, (same & ((1u << lane) - 1u)) == 0u);
+	if(lane == 0) atomicAdd(distinct_sum, (unsigned long long) __popc(leaders));
+}
+
 } // namespace
+
+// Scratch of one sorted batch: [keys | keys' | idx | idx' | count + probe sum (256 B) | CUB temporary storage]
+static size_t sort_layout(uint64_t n, size_t &cub_bytes)
+{
+	cub_bytes = 0;
+	cub::DeviceRadixSort::SortPairs(nullptr, cub_bytes, (const uint32_t *) nullptr, (uint32_t *) nullptr, (const uint32_t *) nullptr, (uint32_t *) nullptr, (int) n);
+	return (size_t) n * 16 + 256 + cub_bytes;
+}
+
+int y4_sort_scratch_reserve(y4gpu_ctx *ctx, Y4SortScratch &sc, uint64_t n)
+{
+	size_t cub_bytes;
+	const size_t need = sort_layout(n, cub_bytes);
+	if(need <= sc.cap) return Y4GPU_OK;
+	if(sc.buf) cudaFree(sc.buf);
+	sc.buf = nullptr; sc.cap = 0;
+	Y4_CUDA(ctx, cudaMalloc(&sc.buf, need));
+	sc.cap = need;
+	return Y4GPU_OK;
+}
+
+// Decides whether a resident batch is worth sorting (mode 2): large enough, tree much larger than L2, and incoherent as laid out.
+// Costs one small kernel and one host synchronisation of `stream`.
+int y4_ray_sort_wanted(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, Y4SortScratch &sc, cudaStream_t stream, bool &want)
+{
+	want = false;
+	if(ctx->ray_sort == 0 || n < (1u << 16) || n >= (1ull << 31)) return Y4GPU_OK;
+	if(ctx->ray_sort == 1) { want = true; return Y4GPU_OK; }
+	if((ctx->n_nodes * 80ull + ctx->n_tri * 48ull) < ctx->ray_sort_min_bvh_bytes) return Y4GPU_OK;
+	const int rc = y4_sort_scratch_reserve(ctx, sc, n);
+	if(rc) return rc;
+	unsigned long long *d_sum = reinterpret_cast<unsigned long long *>(static_cast<char *>(sc.buf) + (size_t) n * 16 + 8);
+	const uint32_t stride = 64, n_groups = (uint32_t) (n / (32ull * stride));
+	if(n_groups == 0) return Y4GPU_OK;
+	const float *bd = ctx->bound;
+	const float sx = 16.f / fmaxf(bd[3] - bd[0], 1e-30f), sy = 16.f / fmaxf(bd[4] - bd[1], 1e-30f), sz = 16.f / fmaxf(bd[5] - bd[2], 1e-30f);
+	Y4_CUDA(ctx, cudaMemsetAsync(d_sum, 0, 8, stream));
+	k_ray_sort_probe<<<(n_groups * 32 + 255) / 256, 256, 0, stream>>>(d_rays, n_groups, stride, bd[0], bd[1], bd[2], sx, sy, sz, d_sum);
+	unsigned long long sum = 0;
+	Y4_CUDA(ctx, cudaMemcpyAsync(&sum, d_sum, 8, cudaMemcpyDeviceToHost, stream));
+	Y4_CUDA(ctx, cudaStreamSynchronize(stream));
+	ctx->last_probe_distinct = (float) ((double) sum / (double) n_groups);
+	want = ctx->last_probe_distinct >= ctx->ray_sort_min_distinct;
+	return Y4GPU_OK;
+}
+
+// keys -> radix sort of (key, ray index) -> k_trace over the sorted index queue; everything on `stream`
+int y4_launch_trace_sorted(y4gpu_ctx *ctx, int kind, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out, unsigned long long *d_work_counter,
+                           Y4SortScratch &sc, cudaStream_t stream)
+{
+	const int rc0 = y4_sort_scratch_reserve(ctx, sc, n);
+	if(rc0) return rc0;
+	size_t cub_bytes;
+	sort_layout(n, cub_bytes);
+	char *base = static_cast<char *>(sc.buf);
+	uint32_t *keys = reinterpret_cast<uint32_t *>(base), *keys2 = keys + n, *idx = keys2 + n, *idx2 = idx + n;
+	uint32_t *count = reinterpret_cast<uint32_t *>(base + (size_t) n * 16);
+	void *cub_tmp = base + (size_t) n * 16 + 256;
+	const int obits = ctx->ray_sort_obits < 1 ? 1 : (ctx->ray_sort_obits > 8 ? 8 : ctx->ray_sort_obits);
+	const float cells = (float) (1 << obits);
+	const float *bd = ctx->bound;
+	const float sx = cells / fmaxf(bd[3] - bd[0], 1e-30f), sy = cells / fmaxf(bd[4] - bd[1], 1e-30f), sz = cells / fmaxf(bd[5] - bd[2], 1e-30f);
+	k_ray_sort_keys<<<(unsigned) ((n + 255) / 256), 256, 0, stream>>>(d_rays, (uint32_t) n, bd[0], bd[1], bd[2], sx, sy, sz, obits, ctx->ray_sort_dir_major, keys, idx, count);
+	Y4_CUDA(ctx, cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, keys, keys2, idx, idx2, (int) n, 0, 3 * obits + 6, stream));
+	TraceArgs a; a.rays = d_rays; a.n = n; a.out = d_out; a.work_counter = d_work_counter; a.visit = nullptr; a.queue = idx2; a.queue_count = count;
+	a.stream = stream; a.max_blocks_per_sm = 0;
+	int rc;
+	if(kind == Y4_TRACE_CLOSEST) rc = launch<Y4_TRACE_CLOSEST, true>(ctx, false, a);
+	else if(kind == Y4_TRACE_SHADOW) rc = launch<Y4_TRACE_SHADOW, true>(ctx, false, a);
+	else { ctx->err = "bad trace kind"; return Y4GPU_ERR_ARG; }
+	if(rc) return rc;
+	Y4_CUDA(ctx, cudaGetLastError());
+	return Y4GPU_OK;
+}
 
 int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out)
 {
@@ -272,7 +399,19 @@ int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays,
 	cudaStream_t st = ctx->stream;
 	Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_work_counter, 0, sizeof(unsigned long long), st));
 	if(counted) Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_visit_counters, 0, 3 * sizeof(unsigned long long), st));
-	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));      // (the probe and the sort are inside the timed span)
+	bool sorted = false;
+	if(!counted) { const int rcs = y4_ray_sort_wanted(ctx, d_rays, n, ctx->sort_scratch, st, sorted); if(rcs) return rcs; }
+	ctx->stats.last_trace_sorted = sorted ? 1 : 0;
+	if(sorted)
+	{
+		const int rcs = y4_launch_trace_sorted(ctx, kind, d_rays, n, d_out, reinterpret_cast<unsigned long long *>(ctx->d_work_counter), ctx->sort_scratch, st);
+		if(rcs) return rcs;
+		Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+		ctx->stats.kernel_launches += 2;        // key kernel + traversal (the radix sort is CUB's)
+		ctx->stats.last_trace_rays = n;
+		return Y4GPU_OK;
+	}
 	TraceArgs a; a.rays = d_rays; a.n = n; a.out = d_out; a.work_counter = reinterpret_cast<unsigned long long *>(ctx->d_work_counter);
 	a.visit = ctx->d_visit_counters; a.queue = nullptr; a.queue_count = nullptr; a.stream = st; a.max_blocks_per_sm = 0;
 	int rc;

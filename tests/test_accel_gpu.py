@@ -137,6 +137,53 @@ def test_transparent_shadows_and_device_resident_batches(sphere):
     assert np.array_equal(got[:, 0], h["t"]) and np.array_equal(got[:, 3].view(np.int32), h["prim"])
 
 
+def test_sorted_ray_order_is_bit_identical_and_the_automatic_mode_leaves_camera_rays_alone(sphere, monkeypatch):
+    """y4gpu_set_ray_sort: tracing a batch in key order (origin cell + direction class, through an index queue) changes only the
+    order in which warps pick rays up -- every hit record equals the unsorted run's, resident and through host buffers."""
+    import torch
+    tris, acc = sphere
+    n = 512
+    prim = scenes.primary_rays(n, n)
+    h = acc.intersect(prim)
+    p, nrm, ok = scenes.hit_points_normals(tris, prim, h["t"], h["prim"])
+    rng = np.random.default_rng(7)
+    batches = {"diffuse": (scenes.diffuse_rays(p, nrm, ok)[rng.permutation(n * n)], acc.intersect),     # shuffled: as incoherent as it gets
+               "shadow": (scenes.shadow_rays(p, ok)[rng.permutation(n * n)], acc.isShadowed), "primary": (prim, acc.intersect)}
+    monkeypatch.setenv("Y4GPU_RAY_SORT_MIN_BVH_MB", "0")       # the automatic mode would skip a BVH that fits L2
+    for name, (rays, fn) in batches.items():
+        acc.set_ray_sort(0)
+        d_rays = torch.from_numpy(rays).cuda()
+        ref = torch.empty((len(rays), 4), dtype=torch.float32, device="cuda")
+        fn(d_rays, ref)
+        acc.synchronize()
+        assert acc.stats()["last_trace_sorted"] == 0
+        for mode in (1, 2):
+            acc.set_ray_sort(mode)
+            out = torch.zeros((len(rays), 4), dtype=torch.float32, device="cuda")
+            fn(d_rays, out)
+            acc.synchronize()
+            st = acc.stats()
+            if mode == 1 or name != "primary":
+                assert st["last_trace_sorted"] == 1, (name, mode, st)
+            else:                                   # camera rays: a handful of distinct keys per warp
+                assert st["last_trace_sorted"] == 0 and st["last_probe_distinct"] < 6, (name, st)
+            if fn == acc.isShadowed:                # any-hit: which blocker is found first may depend on the order, occlusion does not
+                assert torch.equal(out[:, 3].view(torch.int32) >= 0, ref[:, 3].view(torch.int32) >= 0), (name, mode)
+            else:
+                assert torch.equal(out.view(torch.int32), ref.view(torch.int32)), (name, mode)
+        # host buffers (the chunk-pipelined path sorts every chunk on its own stream)
+        acc.set_ray_sort(1)
+        big = np.ascontiguousarray(np.tile(rays, (3, 1)))      # 786 432 rays: several chunks
+        got = fn(big)
+        exp = ref.cpu().numpy()
+        if fn == acc.isShadowed:
+            assert np.array_equal(got["prim"] >= 0, np.tile(exp[:, 3].view(np.int32) >= 0, 3))
+        else:
+            assert np.array_equal(got["t"], np.tile(exp[:, 0], 3)) and np.array_equal(got["prim"], np.tile(exp[:, 3].view(np.int32), 3))
+        assert acc.stats()["last_trace_sorted"] == 1
+    acc.set_ray_sort(2)
+
+
 def test_full_size_c3_properties_and_tree_independence(monkeypatch):
     """BASELINE config C3 at full size (1 M-triangle sphere, 4 Mi + 4 Mi rays here): size-independent properties.
     * a segment is occluded (any-hit) exactly when the closest-hit query over the same range finds something;
