@@ -38,7 +38,8 @@ def sweep(tag, acc, batches, settings):
         d_rays = torch.from_numpy(rays).cuda()
         d_out = torch.empty((len(rays), 4), dtype=torch.float32, device="cuda")
         fn = acc.isShadowed if kind else acc.intersect
-        for mode, obits, dir_major in settings:
+        for setting in settings:
+            mode, obits, dir_major = setting[:3]
             os.environ["Y4GPU_RAY_SORT_OBITS"] = str(obits)
             os.environ["Y4GPU_RAY_SORT_DIR_MAJOR"] = str(dir_major)
             acc.set_ray_sort(mode)
