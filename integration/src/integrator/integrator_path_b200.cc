@@ -220,7 +220,6 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 				m.transparency = get<float>(p, "transparency", 0.f); m.transmit_filter = get<float>(p, "transmit_filter", 1.f);
 				m.translucency = get<float>(p, "translucency", 0.f);
 				if(getStr(p, "diffuse_brdf", "lambert") == "oren_nayar") { m.oren_nayar = 1; m.sigma = get<float>(p, "sigma", 0.1f); }
-				if(m.transparency > 0.00001f && m.specular_reflect > 0.00001f) unsupported("shinydiffusemat '" + mat_names[i] + "': transparency together with specular_reflect");
 				if(get<float>(p, "transparentbias_factor", 0.f) != 0.f) unsupported("shinydiffusemat '" + mat_names[i] + "': transparentbias_factor");
 				if(get<float>(p, "samplingfactor", 1.f) != 1.f || get<int>(p, "additionaldepth", 0) != 0) unsupported("shinydiffusemat '" + mat_names[i] + "': samplingfactor / additionaldepth");
 				if(get<float>(p, "wireframe_amount", 0.f) != 0.f) unsupported("shinydiffusemat '" + mat_names[i] + "': wireframe shading");

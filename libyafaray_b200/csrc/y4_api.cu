@@ -59,6 +59,7 @@ int y4gpu_create(int device, y4gpu_ctx **out)
 	}
 	if(const char *e = getenv("Y4GPU_FETCH_THRESHOLD")) ctx->fetch_threshold = atoi(e);
 	if(const char *e = getenv("Y4GPU_POSTPONE_DIV")) ctx->postpone_div = atoi(e);
+	if(const char *e = getenv("Y4GPU_PT_FETCH_THRESHOLD")) ctx->pt_fetch_threshold = atoi(e);
 	if(const char *e = getenv("Y4GPU_MORTON_SIZED")) ctx->morton_sized = atoi(e);
 	if(const char *e = getenv("Y4GPU_TREELET_DEFER")) { const int k = atoi(e); ctx->treelet_defer = k < 0 ? 0 : (k > 1024 ? 1024 : k); }
 	if(const char *e = getenv("Y4GPU_TREELET")) { const int k = atoi(e); ctx->treelet_leaves = k < 0 ? 0 : (k > 4096 ? 4096 : k); }

@@ -64,6 +64,7 @@ struct y4gpu_ctx
 
 	// warp scheduling knobs of k_trace (env Y4GPU_FETCH_THRESHOLD / Y4GPU_POSTPONE_DIV override)
 	int fetch_threshold = 20, postpone_div = 5, min_blocks = 3;
+	int pt_fetch_threshold = 16;               // refill threshold of the path tracer's wavefront launches (env Y4GPU_PT_FETCH_THRESHOLD; C2 sweep: profiles/r2_v8_sweep_trace_knobs.log)
 	int morton_sized = -1;     // key order: -1 build both binary trees, keep the smaller surface-area sum; 0 plain 21-bit-per-axis Morton keys; 1 extended keys with size bits (env Y4GPU_MORTON_SIZED)
 	int morton_used = 0;       // what the last build chose
 	int treelet_defer = 64;    // sub-ranges of a treelet with at most this many leaves are split by a second, wider launch (env Y4GPU_TREELET_DEFER; 0 = one pass)

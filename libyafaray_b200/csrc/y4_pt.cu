@@ -193,6 +193,13 @@ __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_cons
 constexpr int kCompactThreads = 128;
 constexpr size_t kCompactSmem = (size_t) kCompactThreads * 17 * sizeof(float4);      // 272 B of staged state per thread
 
+// Path-wave traffic of the compacting kernel is touched exactly once per launch: streaming loads / stores (evict-first) keep the
+// small scene tables the stage logic gathers from (materials, lights, per-triangle records, Faure permutations) resident in L1.
+__device__ __forceinline__ float4 ldcs4(const float *p, uint32_t i) { return __ldcs(reinterpret_cast<const float4 *>(p) + i); }
+__device__ __forceinline__ void stcs4(float *p, uint32_t i, float4 v) { __stcs(reinterpret_cast<float4 *>(p) + i, v); }
+__device__ __forceinline__ float4 ldcs_q(const void *p, uint32_t q) { return __ldcs(reinterpret_cast<const float4 *>(p) + q); }      // q-th 16-byte word
+__device__ __forceinline__ void stcs_q(void *p, uint32_t q, float4 v) { __stcs(reinterpret_cast<float4 *>(p) + q, v); }
+
 template<int MINB, bool SPEC>
 __global__ void __launch_bounds__(kCompactThreads, MINB) k_pt_path_compact(const __grid_constant__ Y4PtScene sc, Y4PtWave Wr, Y4PtWave Ww, Y4PtWave W0, Y4PtPass ps,
                                                                            StageArgs a, StageQueues Q, const uint32_t *__restrict__ orig_r, uint32_t *__restrict__ orig_w)
@@ -210,35 +217,39 @@ __global__ void __launch_bounds__(kCompactThreads, MINB) k_pt_path_compact(const
 		S.sray = (Y4Ray *) p; p += 4 * T; S.shit = (Y4Hit *) p; p += 2 * T; S.scontrib = (float *) p; p += 2 * T;
 		S.flags = (uint32_t *) p; S.pix = S.flags + T; S.samp = S.pix + T; S.lnum = S.samp + T;
 	}
-	const uint32_t tid = threadIdx.x, lane = tid & 31u, lt_mask = (1u << lane) - 1u;
+	// regrouping between the two parts of the stage (y4_stage_path_fold / _vertex): a quarter to a third of the paths of a
+	// bounce leave in part 1 (their ray missed, or they only had an estimate to fold in); the rest are packed into full warps
+	__shared__ uint32_t s_cnt[T / 32], s_perm[T], s_push[T];
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5, lt_mask = (1u << lane) - 1u;
 	const uint32_t count = *Q.in_count;
 	const uint32_t stride = gridDim.x * T;
 	const bool closing = a.depth >= sc.bounces;
-	for(uint32_t base = blockIdx.x * T + (tid & ~31u); base < count; base += stride)
+	for(uint32_t cbase = blockIdx.x * T; cbase < count; cbase += stride)       // CTA-uniform trip count (barriers inside)
 	{
-		const uint32_t q = base + lane;
+		const uint32_t q = cbase + tid;
 		const bool have = q < count;
 		uint32_t push = 0u, orig = 0u;
+		bool cont = false;
 		if(have)
 		{
 			const uint32_t j = Q.in_q ? Q.in_q[q] : q;
-			orig = orig_r ? orig_r[j] : j;
-			const uint32_t f = Wr.flags[j];
+			orig = orig_r ? __ldcs(orig_r + j) : j;
+			const uint32_t f = __ldcs(Wr.flags + j);
 			// copy-in: everything y4_stage_path can read, requested together (dense: one coalesced access per field and warp)
-			const float4 v_pcol = ld4(Wr.pcol, j), v_pthr = ld4(Wr.pthr, j), v_sc0 = ld4(Wr.scontrib, j);
+			const float4 v_pcol = ldcs4(Wr.pcol, j), v_pthr = ldcs4(Wr.pthr, j), v_sc0 = ldcs4(Wr.scontrib, j);
 			float4 v_lsamp = v_pcol, v_thr = v_pcol, v_hit = v_pcol, v_r0 = v_pcol, v_r1 = v_pcol;
 			uint32_t pix = 0u, samp = 0u;
 			if(!closing)
 			{
-				v_lsamp = ld4(Wr.lsamp, j); v_thr = ld4(Wr.thr, j); v_hit = *reinterpret_cast<const float4 *>(Wr.hit + j);
-				v_r0 = reinterpret_cast<const float4 *>(Wr.ray + j)[0]; v_r1 = reinterpret_cast<const float4 *>(Wr.ray + j)[1];
-				pix = Wr.pix[j]; samp = Wr.samp[j];
+				v_lsamp = ldcs4(Wr.lsamp, j); v_thr = ldcs4(Wr.thr, j); v_hit = ldcs_q(Wr.hit, j);
+				v_r0 = ldcs_q(Wr.ray, 2u * j); v_r1 = ldcs_q(Wr.ray, 2u * j + 1u);
+				pix = __ldcs(Wr.pix + j); samp = __ldcs(Wr.samp + j);
 			}
-			if(f & Y4_PF_C1) st4(S.scontrib, T + tid, ld4(Wr.scontrib, Wr.n + j));
-			if(f & Y4_PF_S0) *reinterpret_cast<float4 *>(S.shit + tid) = *reinterpret_cast<const float4 *>(Wr.shit + j);
-			if(f & Y4_PF_S1) *reinterpret_cast<float4 *>(S.shit + T + tid) = *reinterpret_cast<const float4 *>(Wr.shit + Wr.n + j);
-			if(f & Y4_PF_LCOL) st4(S.lcol, tid, ld4(Wr.lcol, j));
-			if(sc.n_lights > 1) S.lnum[tid] = Wr.lnum[j];
+			if(f & Y4_PF_C1) st4(S.scontrib, T + tid, ldcs4(Wr.scontrib, Wr.n + j));
+			if(f & Y4_PF_S0) *reinterpret_cast<float4 *>(S.shit + tid) = ldcs_q(Wr.shit, j);
+			if(f & Y4_PF_S1) *reinterpret_cast<float4 *>(S.shit + T + tid) = ldcs_q(Wr.shit, Wr.n + j);
+			if(f & Y4_PF_LCOL) st4(S.lcol, tid, ldcs4(Wr.lcol, j));
+			if(sc.n_lights > 1) S.lnum[tid] = __ldcs(Wr.lnum + j);
 			S.flags[tid] = f; S.pix[tid] = pix; S.samp[tid] = samp;
 			st4(S.pcol, tid, v_pcol); st4(S.pthr, tid, v_pthr); st4(S.scontrib, tid, v_sc0);
 			if(!closing)
@@ -246,8 +257,24 @@ __global__ void __launch_bounds__(kCompactThreads, MINB) k_pt_path_compact(const
 				st4(S.lsamp, tid, v_lsamp); st4(S.thr, tid, v_thr); *reinterpret_cast<float4 *>(S.hit + tid) = v_hit;
 				reinterpret_cast<float4 *>(S.ray + tid)[0] = v_r0; reinterpret_cast<float4 *>(S.ray + tid)[1] = v_r1;
 			}
-			push = y4_stage_path<SPEC>(sc, S, ps, tid, a.depth, a.sub, a.k_prev);
+			cont = y4_stage_path_fold(sc, S, tid, a.depth, a.k_prev);
 		}
+		const uint32_t bal = __ballot_sync(0xffffffffu, cont);
+		if(lane == 0) s_cnt[warp] = (uint32_t) __popc(bal);
+		s_push[tid] = 0u;
+		__syncthreads();
+		uint32_t before = 0u, total = 0u;
+#pragma unroll
+		for(uint32_t w = 0; w < T / 32; ++w) { const uint32_t c = s_cnt[w]; total += c; if(w < warp) before += c; }
+		if(cont) s_perm[before + __popc(bal & lt_mask)] = tid;
+		__syncthreads();
+		if(tid < total)
+		{
+			const uint32_t slot = s_perm[tid];
+			s_push[slot] = y4_stage_path_vertex<SPEC>(sc, S, ps, slot, a.depth, a.sub);
+		}
+		__syncthreads();
+		push = s_push[tid];
 		// queue appends: one 64-bit atomic per warp reserves the path range (low word) and the shadow-ray range (high word)
 		const uint32_t m0 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S0), m1 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S1);
 		const uint32_t mp = __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH);
@@ -268,28 +295,28 @@ __global__ void __launch_bounds__(kCompactThreads, MINB) k_pt_path_compact(const
 			// copy-out to the front of the other path wave
 			const uint32_t o = at_p + __popc(mp & lt_mask);
 			const uint32_t f = S.flags[tid];
-			Ww.flags[o] = f; Ww.pix[o] = S.pix[tid]; Ww.samp[o] = S.samp[tid]; orig_w[o] = orig;
-			if(sc.n_lights > 1) Ww.lnum[o] = S.lnum[tid];
-			st4(Ww.lsamp, o, ld4(S.lsamp, tid)); st4(Ww.thr, o, ld4(S.thr, tid)); st4(Ww.pthr, o, ld4(S.pthr, tid)); st4(Ww.pcol, o, ld4(S.pcol, tid));
-			if(f & Y4_PF_LCOL) st4(Ww.lcol, o, ld4(S.lcol, tid));
-			reinterpret_cast<float4 *>(Ww.ray + o)[0] = reinterpret_cast<const float4 *>(S.ray + tid)[0];
-			reinterpret_cast<float4 *>(Ww.ray + o)[1] = reinterpret_cast<const float4 *>(S.ray + tid)[1];
-			if(f & Y4_PF_DIRECT) st4(Ww.scontrib, o, ld4(S.scontrib, tid));
-			if(f & Y4_PF_C1) st4(Ww.scontrib, Ww.n + o, ld4(S.scontrib, T + tid));
+			__stcs(Ww.flags + o, f); __stcs(Ww.pix + o, S.pix[tid]); __stcs(Ww.samp + o, S.samp[tid]); __stcs(orig_w + o, orig);
+			if(sc.n_lights > 1) __stcs(Ww.lnum + o, S.lnum[tid]);
+			stcs4(Ww.lsamp, o, ld4(S.lsamp, tid)); stcs4(Ww.thr, o, ld4(S.thr, tid)); stcs4(Ww.pthr, o, ld4(S.pthr, tid)); stcs4(Ww.pcol, o, ld4(S.pcol, tid));
+			if(f & Y4_PF_LCOL) stcs4(Ww.lcol, o, ld4(S.lcol, tid));
+			stcs_q(Ww.ray, 2u * o, reinterpret_cast<const float4 *>(S.ray + tid)[0]);
+			stcs_q(Ww.ray, 2u * o + 1u, reinterpret_cast<const float4 *>(S.ray + tid)[1]);
+			if(f & Y4_PF_DIRECT) stcs4(Ww.scontrib, o, ld4(S.scontrib, tid));
+			if(f & Y4_PF_C1) stcs4(Ww.scontrib, Ww.n + o, ld4(S.scontrib, T + tid));
 			if(push & Y4_PUSH_S0)
 			{
-				reinterpret_cast<float4 *>(Ww.sray + o)[0] = reinterpret_cast<const float4 *>(S.sray + tid)[0];
-				reinterpret_cast<float4 *>(Ww.sray + o)[1] = reinterpret_cast<const float4 *>(S.sray + tid)[1];
+				stcs_q(Ww.sray, 2u * o, reinterpret_cast<const float4 *>(S.sray + tid)[0]);
+				stcs_q(Ww.sray, 2u * o + 1u, reinterpret_cast<const float4 *>(S.sray + tid)[1]);
 				Q.sh_q[at_sh + __popc(m0 & lt_mask)] = o;
 			}
 			if(push & Y4_PUSH_S1)
 			{
-				reinterpret_cast<float4 *>(Ww.sray + Ww.n + o)[0] = reinterpret_cast<const float4 *>(S.sray + T + tid)[0];
-				reinterpret_cast<float4 *>(Ww.sray + Ww.n + o)[1] = reinterpret_cast<const float4 *>(S.sray + T + tid)[1];
+				stcs_q(Ww.sray, 2u * (Ww.n + o), reinterpret_cast<const float4 *>(S.sray + T + tid)[0]);
+				stcs_q(Ww.sray, 2u * (Ww.n + o) + 1u, reinterpret_cast<const float4 *>(S.sray + T + tid)[1]);
 				Q.sh_q[at_sh + __popc(m0) + __popc(m1 & lt_mask)] = Ww.n + o;
 			}
 		}
-		else if(have) st4(W0.pcol, orig, ld4(S.pcol, tid));        // the path ended: its path_col goes home to the pixel-sample
+		else if(have) stcs4(W0.pcol, orig, ld4(S.pcol, tid));        // the path ended: its path_col goes home to the pixel-sample
 	}
 }
 
@@ -570,15 +597,16 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		// two specular children per vertex (glass: reflection + refraction): recursiveRaytrace is a tree, walked depth first with a
 		// per-pixel-sample stack (y4_stage_primary3 / y4_stage_finish3)
 		if(mats[m].type == Y4GPU_MAT_GLASS) sc.has_specular = 3;
+		// the same for shinydiffusemat with a mirror AND a transparency component
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].specular_reflect > 0.00001f && mats[m].transparency > 0.00001f) sc.has_specular = 3;
 	}
 	if(sc.has_specular == 3 && params->transp_background) { ctx->err = "transparent background together with glass / mirror + transparency materials is not supported (alpha of a ray tree)"; return Y4GPU_ERR_UNSUPPORTED; }
 	for(uint32_t m = 0; m < n_mat; ++m)
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].transparency > 0.00001f)
 		{
-			// reflect + refract at one vertex = two child rays (a tree, not a chain); filtered shadows need the blockers' colours
-			// (the ray tree could walk reflect + refract, but ShinyDiffuseMaterial::sample with all four components is not restated: y4_mat_sample keeps mirror / transparency in one slot)
-			if(mats[m].specular_reflect > 0.00001f) { ctx->err = "shinydiffusemat with both specular_reflect and transparency is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
-			// filtered shadows take one getTransparency colour per material: a textured diffuse colour would need the blocker's surface point
+			// filtered shadows take one getTransparency colour per material: a Fresnel mirror component makes it depend on the angle,
+			if(params->transp_shadows && mats[m].specular_reflect > 0.00001f && mats[m].fresnel_effect) { ctx->err = "transpShad with a transparent material that also has a Fresnel mirror component is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
+			// a textured diffuse colour would need the blocker's surface point
 			if(params->transp_shadows && mats[m].layer_count > 0) { ctx->err = "textured transparent materials with transpShad are not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 		}
 	// no_recursive makes a mirror hit start sub-paths AND recurse: two branches per vertex, which the linear ray-level chain does not cover
@@ -659,7 +687,9 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	for(uint32_t i = 0; i < n_mat; ++i)
 		if(hm[i].is_transparent)
 		{
-			float accum = 1.f; accum *= hm[i].transparency_strength * accum;
+			float accum = 1.f;
+			if(hm[i].is_mirror) accum = 1.f - 1.f * hm[i].mirror_strength;      // 1 - kr * mirror_strength, kr = 1 without the Fresnel effect (refused with it below)
+			accum *= hm[i].transparency_strength * accum;
 			const C3 tc = y4_shiny_tcol(hm[i]);
 			mat_transp[3 * i] = accum * tc.r; mat_transp[3 * i + 1] = accum * tc.g; mat_transp[3 * i + 2] = accum * tc.b;
 			if(params->transp_shadows) sc.tshadow_filter = 1;

@@ -219,32 +219,32 @@ Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, flo
 	const V3 n = y4_face_forward(sp.ng, sp.n, wo);
 	float accum0, accum1, accum2, accum3;
 	y4_shiny_accumulate(m, wo, n, accum0, accum1, accum2, accum3);
-	// components in c_flags_ order: perfect mirror (Specular | Reflect) or straight transmission (Transmit | Filter) -- the host
-	// refuses materials with both --, translucency (Diffuse | Transmit), Lambert / Oren-Nayar (Diffuse | Reflect)
+	// components in c_flags_ order: perfect mirror (Specular | Reflect), straight transmission (Transmit | Filter),
+	// translucency (Diffuse | Transmit), Lambert / Oren-Nayar (Diffuse | Reflect)
 	const uint32_t mflags = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT, tflags = Y4_BSDF_TRANSMIT | Y4_BSDF_FILTER;
 	const uint32_t lflags = Y4_BSDF_DIFFUSE | Y4_BSDF_TRANSMIT, dflags = Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
 	// (scalars instead of the reference's val[] / width[] / choice[] arrays: same arithmetic, no local memory)
-	const bool mm = m.is_mirror && (flags & mflags) == mflags, tm = !mm && m.is_transparent && (flags & tflags) == tflags;
-	const bool fm = mm || tm;                                    // the component in front of the two diffuse ones
+	const bool mm = m.is_mirror && (flags & mflags) == mflags, tm = m.is_transparent && (flags & tflags) == tflags;
 	const bool lm = m.is_translucent && (flags & lflags) == lflags, dm = m.is_diffuse && (flags & dflags) == dflags;
-	const float accum_f = mm ? accum0 : accum1;
-	float sum = 0.f, val_f = 0.f, val_l = 0.f;
-	if(fm) { sum = xadd(sum, accum_f); val_f = sum; }
+	float sum = 0.f, val_m = 0.f, val_t = 0.f, val_l = 0.f;
+	if(mm) { sum = xadd(sum, accum0); val_m = sum; }
+	if(tm) { sum = xadd(sum, accum1); val_t = sum; }
 	if(lm) { sum = xadd(sum, accum2); val_l = sum; }
 	if(dm) sum = xadd(sum, accum3);
-	if(!(fm || lm || dm) || sum < 0.00001f) return c3f(1.f);
+	if(!(mm || tm || lm || dm) || (double) sum < 0.00001) return c3f(1.f);
 	const float inv_sum = xdiv(1.f, sum);
-	const float wf = xmul(accum_f, inv_sum), wl = xmul(accum2, inv_sum), wd = xmul(accum3, inv_sum);
-	val_f = xmul(val_f, inv_sum); val_l = xmul(val_l, inv_sum);
-	// pick = first matched component with s1 <= val[i], else the last matched one
-	const int pick = (fm && s1 <= val_f) ? 0 : ((lm && s1 <= val_l) ? 1 : (dm ? 2 : (lm ? 1 : 0)));
-	const float wpick = pick == 0 ? wf : (pick == 1 ? wl : wd);
+	const float wm = xmul(accum0, inv_sum), wt = xmul(accum1, inv_sum), wl = xmul(accum2, inv_sum), wd = xmul(accum3, inv_sum);
+	val_m = xmul(val_m, inv_sum); val_t = xmul(val_t, inv_sum); val_l = xmul(val_l, inv_sum);
+	// pick = first matched component with s1 <= val[i] (the last one's val is sum * inv_sum), else the last matched one
+	const int last = dm ? 3 : (lm ? 2 : (tm ? 1 : 0));
+	const int pick = (mm && s1 <= val_m) ? 0 : ((tm && s1 <= val_t) ? 1 : ((lm && s1 <= val_l) ? 2 : ((dm && s1 <= xmul(sum, inv_sum)) ? 3 : last)));
+	const float wpick = pick == 0 ? wm : (pick == 1 ? wt : (pick == 2 ? wl : wd));
 	// s_1 = (s1 - val[previous matched]) / width, or s1 / width for the first matched component
-	const bool has_prev = pick == 1 ? fm : (pick == 2 ? (lm || fm) : false);
-	const float prev = pick == 1 ? val_f : (lm ? val_l : val_f);
+	const bool has_prev = pick == 1 ? mm : (pick == 2 ? (tm || mm) : (pick == 3 ? (lm || tm || mm) : false));
+	const float prev = pick == 1 ? val_m : (pick == 2 ? (tm ? val_t : val_m) : (lm ? val_l : (tm ? val_t : val_m)));
 	const float s_1 = has_prev ? xdiv(xsub(s1, prev), wpick) : xdiv(s1, wpick);
 	C3 scolor = c3f(0.f);
-	if(pick == 0 && tm)
+	if(pick == 1)
 	{
 		wi = xneg(wo);
 		scolor = cscale(y4_shiny_tcol(m), accum1);
@@ -259,7 +259,7 @@ Y4_HD C3 y4_mat_sample(const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, flo
 		scolor = cscale(scolor, xdiv(1.f, fmaxf(fabsf(xdot(sp.n, wi)), 1.0e-6f)));
 		specular = true;
 	}
-	else if(pick == 1)
+	else if(pick == 2)
 	{
 		wi = y4_cos_hemisphere(xneg(n), sp.nu, sp.nv, s_1, s2);
 		if(xmul(cos_ng_wo, xdot(sp.ng, wi)) < 0.f) scolor = cscale(m.color, accum2);

@@ -599,24 +599,29 @@ Y4_HD uint32_t y4_stage_start(const Y4PtScene &sc, const Y4PtWave &W, const Y4Pt
 //   3. BSDF sample -> the next ray in W.ray_next.
 // A path stays on the output queue while it has a ray to trace OR an estimate waiting to be folded in (such a
 // finished path gets an empty ray).  depth == sc.bounces is the closing call: step 1 only.
-template<bool SPEC = true>
-Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub, int k_last)
+// The stage comes in two parts so that a kernel may regroup the vertices between them (k_pt_path_compact: the paths whose ray
+// missed or that only had an estimate to fold leave after part 1; the others are packed into full warps for part 2).
+// Part 1 = step 1 and the ways out; true when the path has a vertex to process.
+Y4_HD bool y4_stage_path_fold(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int depth, int k_last)
 {
 	uint32_t f = W.flags[i];
 	const bool closing = depth >= sc.bounces;
-	// state of this vertex, requested before anything depends on it
-	float4 cache = f4(0.f, 0.f, 0.f, 0.f), thr4 = cache;
-	Y4Hit h; h.t = 0.f; h.bu = 0.f; h.bv = 0.f; h.prim = -1;
-	Y4Ray r = y4_null_ray();
-	uint32_t pix = 0u, samp = 0u;
-	if(!closing)
-	{
-		cache = ld4(W.lsamp, i); thr4 = ld4(W.thr, i); h = ld_hit(W.hit, i); r = ld_ray(W.ray, i); pix = W.pix[i]; samp = W.samp[i];
-	}
 	if(depth > 0 && k_last >= 0) y4_pt_direct_resolve(sc, W, i, f, false, -1, k_last);
+	if(closing || !(f & Y4_PF_ALIVE)) { W.flags[i] = f & ~(uint32_t) Y4_PF_ALIVE; return false; }
+	if(ld_hit(W.hit, i).prim < 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return false; }     // hit background: continue / break
+	W.flags[i] = f;
+	return true;
+}
+// Part 2 = steps 2 and 3.
+template<bool SPEC = true>
+Y4_HD uint32_t y4_stage_path_vertex(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub)
+{
+	uint32_t f = W.flags[i];
+	const float4 cache = ld4(W.lsamp, i), thr4 = ld4(W.thr, i);
+	const Y4Hit h = ld_hit(W.hit, i);
+	const Y4Ray r = ld_ray(W.ray, i);
+	const uint32_t pix = W.pix[i], samp = W.samp[i];
 	uint32_t push = 0u;
-	if(closing || !(f & Y4_PF_ALIVE)) { f &= ~(uint32_t) Y4_PF_ALIVE; W.flags[i] = f; return 0u; }
-	if(h.prim < 0) { W.flags[i] = f & ~(uint32_t) (Y4_PF_ALIVE | Y4_PF_DIRECT); return 0u; }     // hit background: continue / break
 	const Y4Vertex vx = y4_vertex<SPEC>(sc, r, h);
 	C3 thr = c3(thr4.x, thr4.y, thr4.z), emit;
 	const int what = y4_bounce_hit(sc, W, ps, i, pix, samp, f, depth, sub, vx, thr, emit);
@@ -650,6 +655,11 @@ Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtP
 	if(go || (f & Y4_PF_DIRECT)) push |= Y4_PUSH_PATH;
 	W.flags[i] = f;
 	return push;
+}
+template<bool SPEC = true>
+Y4_HD uint32_t y4_stage_path(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int depth, int sub, int k_last)
+{
+	return y4_stage_path_fold(sc, W, i, depth, k_last) ? y4_stage_path_vertex<SPEC>(sc, W, ps, i, depth, sub) : 0u;
 }
 
 // radiance integrate() returns at the current ray level, before recursiveRaytrace's share: col + path_col / n_samples

@@ -238,6 +238,7 @@ struct TraceArgs
 	const uint32_t *queue, *queue_count;
 	cudaStream_t stream;
 	int max_blocks_per_sm;      // 0: as many as fit (persistent grid = one resident wave)
+	int fetch_threshold = 0;    // 0: the context's (ray batches); the path tracer's wavefronts pass their own
 };
 
 template<int KIND, bool COUNT, int MINB, bool QUEUE>
@@ -255,7 +256,7 @@ int launch_k(y4gpu_ctx *ctx, const TraceArgs &a)
 	const uint64_t full = (uint64_t) ctx->sm_count * use_per_sm;     // persistent: one wave of resident CTAs
 	const int grid = (int) (want < full ? want : full);
 	k_trace<KIND, COUNT, MINB, QUEUE><<<grid, kTraceThreads, 0, a.stream>>>(ctx->view(), a.rays, a.n, a.out, a.work_counter, a.visit,
-	                                                                          ctx->fetch_threshold, ctx->postpone_div, a.queue, a.queue_count);
+	                                                                          a.fetch_threshold > 0 ? a.fetch_threshold : ctx->fetch_threshold, ctx->postpone_div, a.queue, a.queue_count);
 	return Y4GPU_OK;
 }
 template<int KIND, bool QUEUE>
@@ -435,7 +436,7 @@ int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_
 {
 	if(n_max == 0) return Y4GPU_OK;
 	TraceArgs a; a.rays = d_rays; a.n = n_max; a.out = d_out; a.work_counter = d_work_counter; a.visit = d_visit; a.queue = d_queue; a.queue_count = d_queue_count;
-	a.stream = stream; a.max_blocks_per_sm = max_blocks_per_sm;
+	a.stream = stream; a.max_blocks_per_sm = max_blocks_per_sm; a.fetch_threshold = ctx->pt_fetch_threshold;
 	int rc;
 	const bool queued = d_queue || d_queue_count;       // a count without a queue: the dense front of a path wave
 	if(kind == Y4_TRACE_CLOSEST) rc = queued ? launch<Y4_TRACE_CLOSEST, true>(ctx, counted, a) : launch<Y4_TRACE_CLOSEST, false>(ctx, counted, a);

@@ -218,8 +218,6 @@ class Interface:
         p = dict(self.params)
         t = p.get("type")
         if t == "shinydiffusemat":
-            if float(p.get("transparency", 0.0)) > 0.00001 and float(p.get("specular_reflect", 0.0)) > 0.00001:
-                raise Y4Error(f"shinydiffusemat '{name}': transparency together with specular_reflect is not supported by the GPU back end")
             if float(p.get("transparentbias_factor", 0.0)) != 0.0:
                 raise Y4Error(f"shinydiffusemat '{name}': transparentbias_factor is not supported by the GPU back end")
             if float(p.get("samplingfactor", 1.0)) != 1.0 or int(p.get("additionaldepth", 0)) != 0:
@@ -942,34 +940,73 @@ def smooth_normals(v: np.ndarray, idx: np.ndarray, angle: float) -> np.ndarray:
     order = np.argsort(idx.reshape(-1), kind="stable")               # incident (face, corner) pairs per vertex, faces in order
     flat_v = idx.reshape(-1)[order]
     starts = np.searchsorted(flat_v, np.arange(len(v) + 1))
-    for pt in range(len(v)):
-        inc = order[starts[pt]:starts[pt + 1]]
-        if len(inc) == 0:
+    valence = np.diff(starts)
+    # vertices of the same valence d are processed together: every step below is the scalar loop's step applied to all of them
+    # at once, so the fp32 order of the sums is unchanged.  Very high valences (sphere poles) take the scalar path.
+    for d in np.unique(valence):
+        d = int(d)
+        if d == 0:
             continue
+        pts = np.nonzero(valence == d)[0]
+        if d > 24 or len(pts) < 8:
+            for pt in pts:
+                _smooth_vertex(order[starts[pt]:starts[pt + 1]], ng, sines, thr, out)
+            continue
+        inc = order[starts[pts][:, None] + np.arange(d)[None, :]]            # [n, d] incident (face, corner) pairs, faces in order
         faces, corners = inc // 3, inc % 3
-        N, S = ng[faces], sines[faces, corners]
-        found = []                                                  # normals already created at this vertex
-        for j in range(len(inc)):
-            dots = (N[:, 0] * N[j, 0] + N[:, 1] * N[j, 1]) + N[:, 2] * N[j, 2]
-            vn = (N[j] * S[j]).astype(f32)
-            smooth = False
-            for k in range(len(inc)):
-                if faces[k] == faces[j]:
-                    continue
-                if dots[k] > thr:
-                    smooth = True
-                    vn = (vn + N[k] * S[k]).astype(f32)
-            if not smooth:
-                continue
-            vn = _normalized(vn[None, :])[0]
-            for e in found:
-                if (vn[0] * e[0] + vn[1] * e[1]) + vn[2] * e[2] > f32(0.999):
-                    vn = e
-                    break
-            else:
-                found.append(vn)
-            out[faces[j], corners[j]] = vn
+        N, S = ng[faces], sines[faces, corners]                              # [n, d, 3], [n, d]
+        NS = (N * S[..., None]).astype(f32)
+        found = np.zeros((len(pts), d, 3), f32)                              # normals already created at each vertex
+        n_found = np.zeros(len(pts), np.int64)
+        rows = np.arange(len(pts))
+        for j in range(d):
+            dots = (N[:, :, 0] * N[:, j, 0][:, None] + N[:, :, 1] * N[:, j, 1][:, None]) + N[:, :, 2] * N[:, j, 2][:, None]     # [n, d]
+            vn = NS[:, j].copy()
+            smooth = np.zeros(len(pts), bool)
+            for k in range(d):
+                take = (faces[:, k] != faces[:, j]) & (dots[:, k] > thr)
+                smooth |= take
+                vn = np.where(take[:, None], (vn + NS[:, k]).astype(f32), vn)
+            vn = _normalized(vn)
+            reuse = np.zeros(len(pts), bool)
+            for e in range(d):                                               # the first earlier normal within 0.999 replaces it
+                cand = found[:, e]
+                hit = smooth & ~reuse & (e < n_found) & ((vn[:, 0] * cand[:, 0] + vn[:, 1] * cand[:, 1]) + vn[:, 2] * cand[:, 2] > f32(0.999))
+                vn = np.where(hit[:, None], cand, vn)
+                reuse |= hit
+            new = smooth & ~reuse
+            found[rows[new], n_found[new]] = vn[new]
+            n_found[new] += 1
+            out[faces[smooth, j], corners[smooth, j]] = vn[smooth]
     return np.ascontiguousarray(out.reshape(n_tri, 9), f32)
+
+
+def _smooth_vertex(inc, ng, sines, thr, out) -> None:
+    """One vertex of smooth_normals' angle-limited branch (scalar form; the vectorised form above follows it step by step)."""
+    f32 = np.float32
+    faces, corners = inc // 3, inc % 3
+    N, S = ng[faces], sines[faces, corners]
+    found = []                                                  # normals already created at this vertex
+    for j in range(len(inc)):
+        dots = (N[:, 0] * N[j, 0] + N[:, 1] * N[j, 1]) + N[:, 2] * N[j, 2]
+        vn = (N[j] * S[j]).astype(f32)
+        smooth = False
+        for k in range(len(inc)):
+            if faces[k] == faces[j]:
+                continue
+            if dots[k] > thr:
+                smooth = True
+                vn = (vn + N[k] * S[k]).astype(f32)
+        if not smooth:
+            continue
+        vn = _normalized(vn[None, :])[0]
+        for e in found:
+            if (vn[0] * e[0] + vn[1] * e[1]) + vn[2] * e[2] > f32(0.999):
+                vn = e
+                break
+        else:
+            found.append(vn)
+        out[faces[j], corners[j]] = vn
 
 
 def _fast_cos_deg(angle: float) -> np.float32:

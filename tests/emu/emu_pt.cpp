@@ -128,6 +128,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].translucency > 0.00001f && !sc.has_specular) sc.has_specular = 1;
 		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f) && sc.has_specular < 2) sc.has_specular = 2;
 		if(mats[m].type == Y4GPU_MAT_GLASS) sc.has_specular = 3;      // ray-tree mode, as y4gpu_pt_set_scene
+		if(mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && mats[m].specular_reflect > 0.00001f && mats[m].transparency > 0.00001f) sc.has_specular = 3;
 	}
 	if(sc.has_specular == 3 && params->transp_background) return -3;
 	// object lights need the general kernel variant as well (not the ray levels)
@@ -168,7 +169,9 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		if(hm[i].is_transparent && params->transp_shadows)      // as y4gpu_pt_set_scene
 		{
 			if(g_mat_transp.empty()) g_mat_transp.assign(3 * (size_t) n_mat, 0.f);
-			float accum = 1.f; accum *= hm[i].transparency_strength * accum;
+			float accum = 1.f;
+			if(hm[i].is_mirror) accum = 1.f - 1.f * hm[i].mirror_strength;      // 1 - kr * mirror_strength, kr = 1 without the Fresnel effect (refused with it below)
+			accum *= hm[i].transparency_strength * accum;
 			const C3 tc = y4_shiny_tcol(hm[i]);
 			g_mat_transp[3 * i] = accum * tc.r; g_mat_transp[3 * i + 1] = accum * tc.g; g_mat_transp[3 * i + 2] = accum * tc.b;
 			sc.tshadow_filter = 1;

@@ -11,6 +11,7 @@ UNMODIFIED reference (oracle/_ref), committed so that the GPU box can check them
 
   pt_glass.npz      <- Cornell box with `glass` objects (PT_GOLDEN_GLASS): reference PathIntegrator / DirectLightIntegrator, deterministic mode
   pt_ibl.npz        <- Cornell box lit by an IBL background light (PT_GOLDEN_IBL), deterministic mode
+  pt_shiny2.npz     <- Cornell box with a shinydiffusemat sheet that is mirror AND transparent (PT_GOLDEN_SHINY2), deterministic mode
   pt_rr.npz         <- Cornell box with the integrator's default Russian roulette (russian_roulette_min_bounces = 0), 1024 spp
 
 Run from the repo root:  python tests/golden/make_golden_large.py [soup|city]
@@ -114,6 +115,32 @@ def make_ibl():
     np.savez_compressed(os.path.join(HERE, "pt_ibl.npz"), **out)
 
 
+# shinydiffusemat with a mirror AND a transparency component: reflect + refract at one vertex (ray tree), all four components in sample() -> pt_shiny2.npz
+PT_GOLDEN_SHINY2 = {
+    "pane_mirror_transp": dict(width=96, height=54, spp=3, bounces=4, pane=dict(transparency=0.6, specular_reflect=0.3, transmit_filter=0.8, color=(0.3, 0.5, 0.9)),
+                               integrator_extra={"raydepth": 3}),
+    "pane_all_four_fresnel_gauss": dict(width=80, height=45, spp=3, bounces=4, filter_type="gauss",
+                                        pane=dict(transparency=0.4, specular_reflect=0.5, fresnel_effect=True, IOR=1.5, translucency=0.3, mirror_color=(1.0, 0.8, 0.6, 1.0)),
+                                        integrator_extra={"raydepth": 4, "caustic_type": "path"}),
+    "pane_and_shiny_walls_transp_shadows": dict(width=80, height=45, spp=2, bounces=3, shiny=dict(specular_reflect=0.25), smooth_sphere=30.0,
+                                                pane=dict(transparency=0.7, specular_reflect=0.2, transmit_filter=0.5, color=(0.9, 0.4, 0.3)),
+                                                integrator_extra={"raydepth": 3, "transpShad": True, "shadowDepth": 3}),
+    "pane_direct_point": dict(width=64, height=36, spp=2, bounces=3, integrator="directlighting", point_light=True,
+                              pane=dict(transparency=0.5, specular_reflect=0.4), integrator_extra={"raydepth": 5}),
+}
+
+
+def make_shiny2():
+    out = {}
+    for key, kw in PT_GOLDEN_SHINY2.items():
+        t0 = time.time()
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print("%s: %.1f s" % (key, time.time() - t0), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_shiny2.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -138,6 +165,8 @@ if __name__ == "__main__":
         make_glass()
     if "ibl" in what:
         make_ibl()
+    if "shiny2" in what:
+        make_shiny2()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

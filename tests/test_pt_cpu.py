@@ -166,7 +166,7 @@ def test_interface_rejects_unsupported_features():
     yi.paramsClearAll()
     yi.paramsSetString("type", "shinydiffusemat")
     yi.paramsSetFloat("transparency", 0.5)
-    yi.paramsSetFloat("specular_reflect", 0.5)      # refraction + reflection at one vertex: two child rays
+    yi.paramsSetFloat("transparentbias_factor", 0.1)   # shifted refraction origins are not restated
     with pytest.raises(Y4Error):
         yi.createMaterial("t")
     yi.paramsClearAll()
@@ -422,11 +422,24 @@ def test_object_light_vs_live_reference(variant):
     assert helpers.psnr(interface.normalize_film(w, rgba), ref) >= 100.0
 
 
-def test_transparency_combinations_outside_the_chain_model_are_rejected():
-    """reflection + refraction at one vertex (two child rays) is refused."""
-    yi = interface.Interface()
-    with pytest.raises(Y4Error, match="specular_reflect"):
-        scenes_pt.cornell_box(yi, width=16, height=9, spp=1, pane=dict(transparency=0.5, specular_reflect=0.2), accelerator="yafaray-b200-bvh8")
+def _shiny2_cfgs():
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_SHINY2
+    return PT_GOLDEN_SHINY2
+
+
+@pytest.mark.parametrize("key", ["pane_mirror_transp", "pane_all_four_fresnel_gauss", "pane_and_shiny_walls_transp_shadows", "pane_direct_point"])
+def test_mirror_and_transparency_on_one_material_vs_golden_reference_render(key):
+    """shinydiffusemat with specular_reflect AND transparency: getSpecular returns a reflected and a refracted ray (the ray tree
+    walks both) and sample() chooses among all four components."""
+    ref = np.load(os.path.join(GOLD, "pt_shiny2.npz"))[key]
+    a = _assemble(**_shiny2_cfgs()[key])
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
 @pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")

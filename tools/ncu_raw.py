@@ -12,7 +12,11 @@ WANT = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio", "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio", "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio", "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio"]
+        "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio", "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
+        "sass__inst_executed_local_loads", "sass__inst_executed_local_stores", "l1tex__t_sectors_pipe_lsu_mem_local_op_ld.sum",
+        "l1tex__t_sectors_pipe_lsu_mem_local_op_ld_lookup_hit.sum", "l1tex__t_sectors_pipe_lsu_mem_local_op_st.sum", "memory_l2_theoretical_sectors_local",
+        "sass__inst_executed_global_loads", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "launch__grid_size", "launch__occupancy_limit_registers",
+        "sm__warps_active.avg.per_cycle_active", "smsp__thread_inst_executed_per_inst_executed.pct"]
 
 for path in sys.argv[1:]:
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout

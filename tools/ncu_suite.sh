@@ -16,10 +16,17 @@ python tools/ncu_raybatch.py $OUT/${TAG}_c5_launches.csv $OUT/rb_classes_c5.json
 # C4 path tracer: the warm-up pass only is enough for per-launch class averages (one pass = ~1000 launches)
 $NCU --metrics $M -c 1100 --log-file $OUT/${TAG}_c4_launches.csv python bench.py --steps 1 --warmup 1 --workload c4 --no-raybatch --no-cpu-baseline --no-e2e --no-profile > $OUT/${TAG}_ncu_c4.log 2>&1; echo "c4 rc=$?"
 python tools/ncu_traffic.py $OUT/${TAG}_c4_launches.csv $OUT/pt_traffic_c4.json "city10000000 3840x2160 spp16 bounces8" > $OUT/${TAG}_c4_classes.txt
-# --set full: one C5 incoherent closest launch, one C4 closest-hit launch + one C4 path stage of a middle bounce, C2 path stage
-ncu --set full --import-source on --clock-control none --kernel-name regex:k_trace --launch-skip 6 -c 1 -o $OUT/${TAG}_full_c5_closest -f python bench.py --steps 1 --warmup 1 --workload c5 --no-cpu-baseline --no-e2e > /dev/null 2>&1; echo "full c5 rc=$?"
-ncu --set full --import-source on --clock-control none --kernel-name regex:k_pt_path_compact --launch-skip 2 -c 1 -o $OUT/${TAG}_full_c4_path -f python bench.py --steps 1 --warmup 1 --workload c4 --no-raybatch --no-cpu-baseline --no-e2e --no-profile > /dev/null 2>&1; echo "full c4 path rc=$?"
-ncu --set full --import-source on --clock-control none --kernel-name regex:k_trace --launch-skip 3 -c 1 -o $OUT/${TAG}_full_c4_closest -f python bench.py --steps 1 --warmup 1 --workload c4 --no-raybatch --no-cpu-baseline --no-e2e --no-profile > /dev/null 2>&1; echo "full c4 closest rc=$?"
-ncu --set full --import-source on --clock-control none --kernel-name regex:k_pt_path_compact --launch-skip 1 -c 1 -o $OUT/${TAG}_full_c2_path -f python bench.py --steps 1 --warmup 1 --no-raybatch --no-cpu-baseline --no-e2e --no-profile > /dev/null 2>&1; echo "full c2 path rc=$?"
+# --set full: three consecutive launches each (read with tools/ncu_raw.py; the longest one is the one quoted):
+#   C3 cosine-diffuse closest-hit batch, C5 incoherent closest-hit batch (sorted order), C4 closest-hit + path kernel of early bounces,
+#   C2 path kernel of early bounces
+FULL="ncu --set full --import-source on --clock-control none -c 3"
+$FULL --kernel-name regex:k_trace --launch-skip 7 -o $OUT/${TAG}_full_c3_trace -f python bench.py --steps 1 --warmup 1 --only-raybatch --no-cpu-baseline --no-e2e > /dev/null 2>&1; echo "full c3 rc=$?"
+$FULL --kernel-name regex:k_trace --launch-skip 4 -o $OUT/${TAG}_full_c5_trace -f python bench.py --steps 1 --warmup 1 --workload c5 --no-cpu-baseline --no-e2e > /dev/null 2>&1; echo "full c5 rc=$?"
+$FULL --kernel-name regex:k_pt_path_compact --launch-skip 0 -o $OUT/${TAG}_full_c4_path -f python bench.py --steps 1 --warmup 1 --workload c4 --no-raybatch --no-cpu-baseline --no-e2e --no-profile > /dev/null 2>&1; echo "full c4 path rc=$?"
+$FULL --kernel-name regex:k_trace --launch-skip 1 -o $OUT/${TAG}_full_c4_trace -f python bench.py --steps 1 --warmup 1 --workload c4 --no-raybatch --no-cpu-baseline --no-e2e --no-profile > /dev/null 2>&1; echo "full c4 trace rc=$?"
+$FULL --kernel-name regex:k_pt_path_compact --launch-skip 0 -o $OUT/${TAG}_full_c2_path -f python bench.py --steps 1 --warmup 1 --no-raybatch --no-cpu-baseline --no-e2e --no-profile > /dev/null 2>&1; echo "full c2 path rc=$?"
+for r in c3_trace c5_trace c4_path c4_trace c2_path; do python tools/ncu_raw.py $OUT/${TAG}_full_$r.ncu-rep > $OUT/${TAG}_full_${r}_raw.txt 2>&1; done
+# memcheck of the smoke scene
+timeout 900 compute-sanitizer --tool memcheck --error-exitcode 3 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/${TAG}_memcheck_smoke.log 2>&1; echo "memcheck rc=$?"; tail -3 $OUT/${TAG}_memcheck_smoke.log
 cat $OUT/${TAG}_c2_classes.txt $OUT/${TAG}_c3_batches.txt $OUT/${TAG}_c5_batches.txt $OUT/${TAG}_c4_classes.txt
 ls -la $OUT/*.ncu-rep
