@@ -9,6 +9,7 @@
 #include "accelerator/accelerator.h"
 #include "geometry/bound.h"
 #include "y4gpu.h"
+#include <atomic>
 #include <vector>
 #include <unordered_map>
 
@@ -44,6 +45,8 @@ class AcceleratorB200 final : public Accelerator
 		std::vector<const Primitive *> primitives_;     // the factory's vector is a temporary: keep a copy (index -> pointer)
 		std::vector<const Material *> materials_;
 		std::vector<float> mat_transparency_;           // [n_mat * 3] Material::getTransparency colour of the transparent materials
+		bool ts_varying_ = false;                       // some transparent material's colour is not one constant: intersectTs refuses
+		mutable std::atomic<bool> ts_error_logged_{false};
 		Bound bound_;
 };
 

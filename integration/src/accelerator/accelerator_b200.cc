@@ -82,6 +82,7 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 	// Material::getTransparency of the transparent materials, evaluated by the reference's own code on one surface point.  The
 	// device multiplies one colour per material, so a colour that varies over the surface cannot be reproduced: refuse it.
 	std::vector<float> mat_transparency(materials.size() * 3, 0.f);
+	bool ts_varying = false;
 	for(size_t mi = 0; mi < materials.size(); ++mi)
 	{
 		if(!materials[mi] || !materials[mi]->isTransparent()) continue;
@@ -104,9 +105,10 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 		}
 		if(std::abs(colour[0].r_ - colour[1].r_) > 1e-6f || std::abs(colour[0].g_ - colour[1].g_) > 1e-6f || std::abs(colour[0].b_ - colour[1].b_) > 1e-6f)
 		{
-			logger.logError("AcceleratorB200: a transparent material's shadow colour varies over the surface / with the direction (textured or mirror + transparency): not supported");
-			y4gpu_destroy(ctx);
-			return nullptr;
+			// only intersectTs needs the table: closest-hit / shadow queries (and PathIntegratorB200, which filters shadows on the
+			// device from its own per-material table and refuses what that cannot express) are unaffected
+			logger.logWarning("AcceleratorB200: a transparent material's shadow colour varies over the surface / with the direction (textured, or Fresnel mirror + transparency): intersectTs (transparent shadows) will fail on this scene");
+			ts_varying = true;
 		}
 		mat_transparency[3 * mi] = colour[0].r_; mat_transparency[3 * mi + 1] = colour[0].g_; mat_transparency[3 * mi + 2] = colour[0].b_;
 	}
@@ -121,7 +123,9 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 	y4gpu_stats st;
 	y4gpu_get_stats(ctx, &st);
 	logger.logInfo("AcceleratorB200: ", n, " triangles, ", st.n_nodes, " BVH8 nodes in ", st.bvh_levels, " levels, built in ", st.build_ms, " ms on the GPU");
-	return new AcceleratorB200(logger, ctx, primitives, std::move(materials), std::move(mat_transparency), Bound{{b[0], b[1], b[2]}, {b[3], b[4], b[5]}});
+	auto *acc = new AcceleratorB200(logger, ctx, primitives, std::move(materials), std::move(mat_transparency), Bound{{b[0], b[1], b[2]}, {b[3], b[4], b[5]}});
+	acc->ts_varying_ = ts_varying;
+	return acc;
 }
 
 AcceleratorB200::~AcceleratorB200() { y4gpu_destroy(ctx_); }
@@ -173,6 +177,13 @@ AcceleratorIntersectData AcceleratorB200::intersectS(const Ray &ray, float t_max
 AcceleratorTsIntersectData AcceleratorB200::intersectTs(const Ray &ray, int max_depth, float dist, float, const Camera *) const
 {
 	AcceleratorTsIntersectData d;
+	if(ts_varying_)
+	{
+		// no CPU fallback and no approximation: the query fails loudly and lets no light through
+		if(!ts_error_logged_.exchange(true)) logger_.logError("AcceleratorB200::intersectTs: a transparent material's shadow colour is not constant per material on this scene: not supported by the GPU back end");
+		d.hit_ = true;
+		return d;
+	}
 	const y4gpu_ray r = toRay(ray, ray.tmin_, dist);
 	y4gpu_tshit h;
 	if(y4gpu_trace_tshadow_inner(ctx_, &r, 1, max_depth, mat_transparency_.data(), (uint32_t) materials_.size(), &h) != Y4GPU_OK)

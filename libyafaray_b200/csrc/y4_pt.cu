@@ -217,19 +217,17 @@ __global__ void __launch_bounds__(kCompactThreads, MINB) k_pt_path_compact(const
 		S.sray = (Y4Ray *) p; p += 4 * T; S.shit = (Y4Hit *) p; p += 2 * T; S.scontrib = (float *) p; p += 2 * T;
 		S.flags = (uint32_t *) p; S.pix = S.flags + T; S.samp = S.pix + T; S.lnum = S.samp + T;
 	}
-	// regrouping between the two parts of the stage (y4_stage_path_fold / _vertex): a quarter to a third of the paths of a
-	// bounce leave in part 1 (their ray missed, or they only had an estimate to fold in); the rest are packed into full warps
-	__shared__ uint32_t s_cnt[T / 32], s_perm[T], s_push[T];
-	const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5, lt_mask = (1u << lane) - 1u;
+	const uint32_t tid = threadIdx.x, lane = tid & 31u, lt_mask = (1u << lane) - 1u;
 	const uint32_t count = *Q.in_count;
 	const uint32_t stride = gridDim.x * T;
 	const bool closing = a.depth >= sc.bounces;
-	for(uint32_t cbase = blockIdx.x * T; cbase < count; cbase += stride)       // CTA-uniform trip count (barriers inside)
+	// (tried: regrouping the paths that go on after the fold into full warps inside the CTA, between y4_stage_path_fold and
+	// y4_stage_path_vertex -- three barriers per iteration cost more than the 30 % idle lanes: 18.0 -> 18.6 ms per pass)
+	for(uint32_t base = blockIdx.x * T + (tid & ~31u); base < count; base += stride)
 	{
-		const uint32_t q = cbase + tid;
+		const uint32_t q = base + lane;
 		const bool have = q < count;
 		uint32_t push = 0u, orig = 0u;
-		bool cont = false;
 		if(have)
 		{
 			const uint32_t j = Q.in_q ? Q.in_q[q] : q;
@@ -257,24 +255,8 @@ __global__ void __launch_bounds__(kCompactThreads, MINB) k_pt_path_compact(const
 				st4(S.lsamp, tid, v_lsamp); st4(S.thr, tid, v_thr); *reinterpret_cast<float4 *>(S.hit + tid) = v_hit;
 				reinterpret_cast<float4 *>(S.ray + tid)[0] = v_r0; reinterpret_cast<float4 *>(S.ray + tid)[1] = v_r1;
 			}
-			cont = y4_stage_path_fold(sc, S, tid, a.depth, a.k_prev);
+			push = y4_stage_path<SPEC>(sc, S, ps, tid, a.depth, a.sub, a.k_prev);
 		}
-		const uint32_t bal = __ballot_sync(0xffffffffu, cont);
-		if(lane == 0) s_cnt[warp] = (uint32_t) __popc(bal);
-		s_push[tid] = 0u;
-		__syncthreads();
-		uint32_t before = 0u, total = 0u;
-#pragma unroll
-		for(uint32_t w = 0; w < T / 32; ++w) { const uint32_t c = s_cnt[w]; total += c; if(w < warp) before += c; }
-		if(cont) s_perm[before + __popc(bal & lt_mask)] = tid;
-		__syncthreads();
-		if(tid < total)
-		{
-			const uint32_t slot = s_perm[tid];
-			s_push[slot] = y4_stage_path_vertex<SPEC>(sc, S, ps, slot, a.depth, a.sub);
-		}
-		__syncthreads();
-		push = s_push[tid];
 		// queue appends: one 64-bit atomic per warp reserves the path range (low word) and the shadow-ray range (high word)
 		const uint32_t m0 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S0), m1 = __ballot_sync(0xffffffffu, push & Y4_PUSH_S1);
 		const uint32_t mp = __ballot_sync(0xffffffffu, push & Y4_PUSH_PATH);

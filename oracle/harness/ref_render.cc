@@ -58,7 +58,8 @@ int main(int argc, char **argv)
 	if(argc < 2) { fprintf(stderr, "usage: %s scene.script\n", argv[0]); return 2; }
 	std::ifstream in(argv[1]);
 	if(!in) { fprintf(stderr, "cannot open %s\n", argv[1]); return 2; }
-	yafaray_Interface_t *yi = yafaray_createInterface(YAFARAY_INTERFACE_FOR_RENDERING, nullptr, nullptr, nullptr, YAFARAY_DISPLAY_CONSOLE_HIDDEN);
+	yafaray_Interface_t *yi = yafaray_createInterface(YAFARAY_INTERFACE_FOR_RENDERING, nullptr, nullptr, nullptr,
+	                                                 getenv("REF_RENDER_VERBOSITY") ? YAFARAY_DISPLAY_CONSOLE_NORMAL : YAFARAY_DISPLAY_CONSOLE_HIDDEN);
 	const char *verb = getenv("REF_RENDER_VERBOSITY");
 	yafaray_setConsoleVerbosityLevel(yi, yafaray_logLevelFromString(verb ? verb : "mute"));
 	yafaray_setLogVerbosityLevel(yi, yafaray_logLevelFromString("mute"));
