@@ -104,6 +104,17 @@ void y4gpu_host_free(void *p);
  * PrimitiveInstance does per test, primitive_instance.cc:43-51), in primitive order.
  * flags: n_tri words or NULL (all visible, opaque, material 0).  Host or device pointers. */
 int y4gpu_upload_triangles(y4gpu_ctx *ctx, const float *v_xyz, const uint32_t *flags, uint64_t n_tri);
+/* Instanced geometry (yafaray_addInstance; PrimitiveInstance / ObjectInstance, primitive_instance.cc:43-51,
+ * object_instance.cc:25-33): base meshes in OBJECT space, uploaded once, and instances that place them with the rows 0..2 of
+ * the reference's Matrix4 (obj_to_world).  A plain, un-instanced object is an instance with identity = 1 of a mesh given in world
+ * space.  Primitive indices run over the instances in the order given (instance i's triangle k = first_prim(i) + k), i.e. exactly
+ * the indices of the flattened scene; results are bit-identical to uploading the flattened triangles: the device keeps the
+ * meshes once (a top-level BVH8 over instances, one bottom-level BVH8 per mesh) and transforms a triangle's vertices to world
+ * space per test like the reference does.  flags may be NULL per mesh (all visible, opaque, material 0).
+ * Not available on such a scene: y4gpu_trace_tshadow* (filter colours) and the visit counters of y4gpu_trace_counted. */
+typedef struct y4gpu_mesh { const float *v_xyz; const uint32_t *flags; uint64_t n_tri; } y4gpu_mesh;
+typedef struct y4gpu_instance { uint32_t mesh; uint32_t identity; float obj_to_world[12]; } y4gpu_instance;
+int y4gpu_upload_instanced(y4gpu_ctx *ctx, const y4gpu_mesh *meshes, uint32_t n_mesh, const y4gpu_instance *instances, uint32_t n_inst);
 int y4gpu_build(y4gpu_ctx *ctx, const y4gpu_build_params *params /* nullable */);
 /* tree bound with the reference's 0.1 % inflation (accelerator_kdtree.cc:81-85): lo xyz, hi xyz */
 int y4gpu_get_bound(const y4gpu_ctx *ctx, float out_bound[6]);

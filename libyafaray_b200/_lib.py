@@ -38,6 +38,14 @@ class Stats(C.Structure):
     ]  # fmt: skip
 
 
+class Mesh(C.Structure):          # y4gpu_mesh
+    _fields_ = [("v_xyz", C.c_void_p), ("flags", C.c_void_p), ("n_tri", C.c_uint64)]
+
+
+class Instance(C.Structure):      # y4gpu_instance
+    _fields_ = [("mesh", C.c_uint32), ("identity", C.c_uint32), ("obj_to_world", C.c_float * 12)]
+
+
 class PtMaterial(C.Structure):
     _fields_ = [("type", C.c_int32), ("color", C.c_float * 3), ("diffuse_reflect", C.c_float), ("emit", C.c_float),
                 ("oren_nayar", C.c_int32), ("sigma", C.c_float), ("double_sided", C.c_int32), ("receive_shadows", C.c_int32),
@@ -130,7 +138,7 @@ _lib = None
 EXPORTED = [
     "y4gpu_create", "y4gpu_destroy", "y4gpu_last_error", "y4gpu_device_count",
     "y4gpu_set_stream", "y4gpu_host_alloc", "y4gpu_host_free",
-    "y4gpu_upload_triangles", "y4gpu_build", "y4gpu_get_bound",
+    "y4gpu_upload_triangles", "y4gpu_upload_instanced", "y4gpu_build", "y4gpu_get_bound",
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow", "y4gpu_trace_tshadow_inner", "y4gpu_trace_noalloc",
     "y4gpu_set_ray_sort", "y4gpu_get_stats", "y4gpu_synchronize",
     "y4gpu_pt_set_textures", "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
@@ -163,6 +171,8 @@ def lib() -> C.CDLL:
     L.y4gpu_host_free.restype = None
     L.y4gpu_upload_triangles.argtypes = [vp, vp, vp, u64]
     L.y4gpu_upload_triangles.restype = i32
+    L.y4gpu_upload_instanced.argtypes = [vp, C.POINTER(Mesh), u32, C.POINTER(Instance), u32]
+    L.y4gpu_upload_instanced.restype = i32
     L.y4gpu_build.argtypes = [vp, C.POINTER(BuildParams)]
     L.y4gpu_build.restype = i32
     L.y4gpu_get_bound.argtypes = [vp, C.POINTER(C.c_float * 6)]

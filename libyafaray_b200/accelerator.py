@@ -49,7 +49,7 @@ class AcceleratorB200:
     """BVH8 accelerator resident in HBM; primitives = float32 [n_tri, 9] world-space triangles
     in the order of the vector handed to Accelerator::factory (primitive index == row)."""
 
-    def __init__(self, primitives: np.ndarray, flags: Optional[np.ndarray] = None, leaf_max: int = 0, device: int = 0):
+    def __init__(self, primitives: Optional[np.ndarray], flags: Optional[np.ndarray] = None, leaf_max: int = 0, device: int = 0):
         self._L = _lib.lib()
         self._ctx = C.c_void_p()
         rc = self._L.y4gpu_create(device, C.byref(self._ctx))
@@ -57,7 +57,36 @@ class AcceleratorB200:
             msg = self._L.y4gpu_last_error(None)
             self._ctx = C.c_void_p()
             raise Y4Error(f"y4gpu_create failed (rc={rc}): {msg.decode() if msg else ''}")
-        self.rebuild(primitives, flags, leaf_max)
+        if primitives is not None:
+            self.rebuild(primitives, flags, leaf_max)
+
+    @classmethod
+    def from_instances(cls, meshes, instances, mesh_flags=None, leaf_max: int = 0, device: int = 0) -> "AcceleratorB200":
+        """Two-level accelerator (yafaray_addInstance: PrimitiveInstance / ObjectInstance).  meshes: [n_i, 9] fp32 arrays in object
+        space; instances: (mesh index, 3x4 obj_to_world rows of the reference's Matrix4, or None for a plain world-space object),
+        in primitive order.  Hits are bit-identical to the flattened scene's (include/y4gpu.h: y4gpu_upload_instanced)."""
+        acc = cls(None, device=device)
+        acc.rebuild_instances(meshes, instances, mesh_flags, leaf_max)
+        return acc
+
+    def rebuild_instances(self, meshes, instances, mesh_flags=None, leaf_max: int = 0) -> None:
+        ms = [np.ascontiguousarray(m, dtype=np.float32).reshape(-1, 9) for m in meshes]
+        fs = [None if (mesh_flags is None or mesh_flags[i] is None) else np.ascontiguousarray(mesh_flags[i], dtype=np.uint32).reshape(-1) for i in range(len(ms))]
+        M = (_lib.Mesh * max(1, len(ms)))()
+        for i, m in enumerate(ms):
+            if fs[i] is not None and len(fs[i]) != len(m):
+                raise Y4Error("mesh flags must have one word per triangle")
+            M[i].v_xyz, M[i].flags, M[i].n_tri = m.ctypes.data, (fs[i].ctypes.data if fs[i] is not None else None), len(m)
+        I = (_lib.Instance * max(1, len(instances)))()
+        ident = (1.0, 0.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 0.0, 1.0, 0.0)
+        for i, (mesh, mat) in enumerate(instances):
+            I[i].mesh, I[i].identity = int(mesh), 1 if mat is None else 0
+            I[i].obj_to_world[:] = ident if mat is None else [float(x) for x in np.asarray(mat, np.float32).reshape(12)]
+        self.n_primitives = int(sum(len(ms[int(mesh)]) for mesh, _ in instances))
+        _lib.check(self._ctx, self._L.y4gpu_upload_instanced(self._ctx, M, len(ms), I, len(instances)), "y4gpu_upload_instanced")
+        bp = _lib.BuildParams()
+        bp.leaf_max = leaf_max
+        _lib.check(self._ctx, self._L.y4gpu_build(self._ctx, C.byref(bp)), "y4gpu_build")
 
     def rebuild(self, primitives: np.ndarray, flags: Optional[np.ndarray] = None, leaf_max: int = 0) -> None:
         """Upload a new primitive list into the same context and build its BVH8 (device arrays are reused when the

@@ -5,7 +5,7 @@
 #include <cstdlib>
 
 static std::string g_create_err;
-extern "C" { static void ray_sort_env(y4gpu_ctx *ctx); }
+extern "C" { static void ray_sort_env(y4gpu_ctx *ctx); static void free_meshes(y4gpu_ctx *ctx); }
 
 extern "C" { static void slot_free_all(y4gpu_ctx *ctx); }
 
@@ -82,6 +82,7 @@ void y4gpu_destroy(y4gpu_ctx *ctx)
 	cudaFree(ctx->d_verts); cudaFree(ctx->d_flags); cudaFree(ctx->d_nodes); cudaFree(ctx->d_tris);
 	cudaFree(ctx->d_rays); cudaFree(ctx->d_hits); cudaFree(ctx->d_work_counter); cudaFree(ctx->d_visit_counters); cudaFree(ctx->d_consts);
 	cudaFree(ctx->d_mat_transp); cudaFree(ctx->sort_scratch.buf);
+	cudaFree(ctx->d_mesh_verts); cudaFree(ctx->d_mesh_flags); y4_free_two_level(ctx);
 	if(ctx->ev0) cudaEventDestroy(ctx->ev0);
 	if(ctx->ev1) cudaEventDestroy(ctx->ev1);
 	if(ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -105,6 +106,7 @@ int y4gpu_upload_triangles(y4gpu_ctx *ctx, const float *v_xyz, const uint32_t *f
 	std::lock_guard<std::mutex> lock(ctx->mtx);
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	// a re-upload of the same size (animation frame, repeated render) reuses the device arrays
+	if(ctx->two_level) { free_meshes(ctx); ctx->n_tri = 0; }
 	const bool reuse = n_tri && n_tri == ctx->n_tri && ctx->d_verts && (!flags == !ctx->d_flags);
 	ctx->built = false;
 	y4_pt_invalidate(ctx);
@@ -126,6 +128,78 @@ int y4gpu_upload_triangles(y4gpu_ctx *ctx, const float *v_xyz, const uint32_t *f
 	return Y4GPU_OK;
 }
 
+static void free_meshes(y4gpu_ctx *ctx)
+{
+	cudaFree(ctx->d_mesh_verts); cudaFree(ctx->d_mesh_flags);
+	ctx->d_mesh_verts = nullptr; ctx->d_mesh_flags = nullptr;
+	ctx->mesh_first.clear(); ctx->h_inst.clear();
+	y4_free_two_level(ctx);
+	ctx->two_level = false;
+}
+
+int y4gpu_upload_instanced(y4gpu_ctx *ctx, const y4gpu_mesh *meshes, uint32_t n_mesh, const y4gpu_instance *instances, uint32_t n_inst)
+{
+	if(!ctx || (n_mesh && !meshes) || (n_inst && !instances)) return Y4GPU_ERR_ARG;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	ctx->built = false;
+	y4_pt_invalidate(ctx);
+	free_meshes(ctx);
+	cudaFree(ctx->d_verts); cudaFree(ctx->d_flags); cudaFree(ctx->d_nodes); cudaFree(ctx->d_tris);
+	ctx->d_verts = nullptr; ctx->d_flags = nullptr; ctx->d_nodes = nullptr; ctx->d_tris = nullptr; ctx->n_tri = 0; ctx->n_nodes = 0;
+	std::vector<uint64_t> first(n_mesh + 1, 0);
+	bool any_flags = false;
+	for(uint32_t i = 0; i < n_mesh; ++i)
+	{
+		if(meshes[i].n_tri && !meshes[i].v_xyz) { ctx->err = "mesh without vertices"; return Y4GPU_ERR_ARG; }
+		first[i + 1] = first[i] + meshes[i].n_tri;
+		any_flags = any_flags || meshes[i].flags;
+	}
+	uint64_t total = 0;
+	for(uint32_t i = 0; i < n_inst; ++i)
+	{
+		if(instances[i].mesh >= n_mesh) { ctx->err = "instance refers to a mesh that was not given"; return Y4GPU_ERR_ARG; }
+		total += meshes[instances[i].mesh].n_tri;
+	}
+	if(total > 0x3fffffffull || first[n_mesh] > 0x3fffffffull) { ctx->err = "too many triangles (max 2^30-1)"; return Y4GPU_ERR_ARG; }
+	ctx->two_level = true;
+	if(first[n_mesh])
+	{
+		Y4_CUDA(ctx, cudaMalloc(&ctx->d_mesh_verts, first[n_mesh] * 9 * sizeof(float)));
+		if(any_flags) Y4_CUDA(ctx, cudaMalloc(&ctx->d_mesh_flags, first[n_mesh] * sizeof(uint32_t)));
+		for(uint32_t i = 0; i < n_mesh; ++i)
+		{
+			const uint64_t n = meshes[i].n_tri;
+			if(!n) continue;
+			Y4_CUDA(ctx, cudaMemcpyAsync(ctx->d_mesh_verts + 9ull * first[i], meshes[i].v_xyz, n * 9 * sizeof(float), cudaMemcpyDefault, ctx->stream));
+			if(any_flags)
+			{
+				if(meshes[i].flags) Y4_CUDA(ctx, cudaMemcpyAsync(ctx->d_mesh_flags + first[i], meshes[i].flags, n * sizeof(uint32_t), cudaMemcpyDefault, ctx->stream));
+				else
+				{
+					std::vector<uint32_t> def(n, (uint32_t) Y4_TRI_DEFAULT_FLAGS);
+					Y4_CUDA(ctx, cudaMemcpy(ctx->d_mesh_flags + first[i], def.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+				}
+			}
+		}
+		Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	ctx->mesh_first = first;
+	ctx->h_inst.resize(n_inst);
+	uint32_t first_prim = 0;
+	for(uint32_t i = 0; i < n_inst; ++i)
+	{
+		Y4Inst &in = ctx->h_inst[i];
+		memset(&in, 0, sizeof(in));
+		memcpy(in.m, instances[i].obj_to_world, sizeof(in.m));
+		in.mesh = instances[i].mesh; in.identity = instances[i].identity ? 1u : 0u;
+		in.n_tri = (uint32_t) meshes[in.mesh].n_tri; in.first_prim = first_prim; in.vert_first = (uint32_t) first[in.mesh];
+		first_prim += in.n_tri;
+	}
+	ctx->n_tri = total;
+	return Y4GPU_OK;
+}
+
 int y4gpu_build(y4gpu_ctx *ctx, const y4gpu_build_params *params)
 {
 	if(!ctx) return Y4GPU_ERR_ARG;
@@ -133,7 +207,7 @@ int y4gpu_build(y4gpu_ctx *ctx, const y4gpu_build_params *params)
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	int leaf_max = params && params->leaf_max ? params->leaf_max : 1;
 	y4_pt_invalidate(ctx);
-	return y4_build_bvh(ctx, leaf_max);
+	return ctx->two_level ? y4_build_two_level(ctx, leaf_max) : y4_build_bvh(ctx, leaf_max);
 }
 
 int y4gpu_get_bound(const y4gpu_ctx *ctx, float out_bound[6])

@@ -323,18 +323,19 @@ template<typename T> struct DevBuf
 
 } // namespace
 
-int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
+// One BVH8 over `n` triangles (world space for a flat scene and for the proxies of a top-level tree, object space for a
+// base mesh).  The caller owns out.nodes / out.tris.
+struct Y4Built
 {
-	const int n = (int) ctx->n_tri;
-	cudaStream_t st = ctx->stream;
-	if(ctx->d_nodes) { cudaFree(ctx->d_nodes); ctx->d_nodes = nullptr; }
-	if(ctx->d_tris) { cudaFree(ctx->d_tris); ctx->d_tris = nullptr; }
-	ctx->n_nodes = 0;
-	for(int k = 0; k < 6; ++k) ctx->raw_bound[k] = ctx->bound[k] = 0.f;
-	if(n == 0) { ctx->built = true; return Y4GPU_OK; }
-	if(leaf_max < 1 || leaf_max > 3) { ctx->err = "leaf_max must be 1..3"; return Y4GPU_ERR_ARG; }
+	Y4U4 *nodes = nullptr; Y4Tri *tris = nullptr;
+	uint64_t n_nodes = 0;
+	int levels = 0, morton_used = 0;
+	float raw[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+};
 
-	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+static int build_core(y4gpu_ctx *ctx, const float *d_verts, const uint32_t *d_flags, int n, int leaf_max, Y4Built &res)
+{
+	cudaStream_t st = ctx->stream;
 	DevBuf<Y4Box> tb, box;
 	DevBuf<uint32_t> scene_enc, vals_a, vals_b, counters, items_a, items_b;
 	DevBuf<uint64_t> keys_a, keys_b;
@@ -351,22 +352,15 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 	Y4_CUDA(ctx, cudaMemcpyAsync(scene_enc.p, enc_init, sizeof(enc_init), cudaMemcpyHostToDevice, st));
 	const int tpb = 256;
 	const int grid_n = (n + tpb - 1) / tpb;
-	k_tri_boxes<<<min(grid_n, ctx->sm_count * 8), tpb, 0, st>>>(ctx->d_verts, n, tb.p, scene_enc.p);
+	k_tri_boxes<<<min(grid_n, ctx->sm_count * 8), tpb, 0, st>>>(d_verts, n, tb.p, scene_enc.p);
 	uint32_t enc_out[6];
 	Y4_CUDA(ctx, cudaMemcpyAsync(enc_out, scene_enc.p, sizeof(enc_out), cudaMemcpyDeviceToHost, st));
 	Y4_CUDA(ctx, cudaStreamSynchronize(st));
 	Y4Box scene;
 	scene.lox = dec_f(enc_out[0]); scene.loy = dec_f(enc_out[1]); scene.loz = dec_f(enc_out[2]);
 	scene.hix = dec_f(enc_out[3]); scene.hiy = dec_f(enc_out[4]); scene.hiz = dec_f(enc_out[5]);
-	ctx->raw_bound[0] = scene.lox; ctx->raw_bound[1] = scene.loy; ctx->raw_bound[2] = scene.loz;
-	ctx->raw_bound[3] = scene.hix; ctx->raw_bound[4] = scene.hiy; ctx->raw_bound[5] = scene.hiz;
-	// reference tree bound inflation, accelerator_kdtree.cc:81-85 (double arithmetic, stored as float)
-	for(int a = 0; a < 3; ++a)
-	{
-		const double foo = (double) (ctx->raw_bound[3 + a] - ctx->raw_bound[a]) * 0.001;
-		ctx->bound[a] = (float) ((double) ctx->raw_bound[a] - foo);
-		ctx->bound[3 + a] = (float) ((double) ctx->raw_bound[3 + a] + foo);
-	}
+	res.raw[0] = scene.lox; res.raw[1] = scene.loy; res.raw[2] = scene.loz;
+	res.raw[3] = scene.hix; res.raw[4] = scene.hiy; res.raw[5] = scene.hiz;
 
 	// Key order: plain 63-bit Morton codes of the box centres, or extended codes that interleave one size bit per octree
 	// level (large triangles leave their neighbours' subtree early).  Which one gives the cheaper tree depends on the
@@ -440,7 +434,7 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 			ctx->stats.kernel_launches++;
 		}
 	}
-	ctx->morton_used = built_sized;
+	res.morton_used = built_sized;
 	if(getenv("Y4GPU_DEBUG")) fprintf(stderr, "[y4gpu] build: n=%d key order %s (internal area plain %.6g, sized %.6g)\n", n, built_sized ? "sized" : "plain", area[0], area[1]);
 
 	// collapse into BVH8
@@ -448,7 +442,7 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 	Y4U4 *nodes = nullptr; Y4Tri *tris = nullptr;
 	Y4_CUDA(ctx, cudaMalloc(&nodes, max_nodes * Y4_NODE_WORDS * sizeof(Y4U4)));
 	if(cudaMalloc(&tris, (size_t) n * sizeof(Y4Tri)) != cudaSuccess) { cudaFree(nodes); ctx->err = "cudaMalloc tris failed"; return Y4GPU_ERR_CUDA; }
-	ctx->d_nodes = nodes; ctx->d_tris = tris;
+	res.nodes = nodes; res.tris = tris;
 	Y4_CUDA(ctx, items_a.alloc(2ull * n + 2)); Y4_CUDA(ctx, items_b.alloc(2ull * n + 2));
 	const uint32_t init_counters[4] = {1u, 0u, 0u, 0u};   // node_counter, tri_counter, next_count, pad
 	Y4_CUDA(ctx, cudaMemcpyAsync(counters.p, init_counters, sizeof(init_counters), cudaMemcpyHostToDevice, st));
@@ -465,49 +459,246 @@ int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
 		out.nodes = nodes; out.tris = tris; out.node_counter = counters.p; out.tri_counter = counters.p + 1;
 		out.next_items = nxt; out.next_count = counters.p + 2;
 		Y4_CUDA(ctx, cudaMemsetAsync(counters.p + 2, 0, sizeof(uint32_t), st));
-		k_collapse<<<(count + 127) / 128, 128, 0, st>>>(bt, leaf_max, cur, count, ctx->d_verts, ctx->d_flags, out);
+		k_collapse<<<(count + 127) / 128, 128, 0, st>>>(bt, leaf_max, cur, count, d_verts, d_flags, out);
 		Y4_CUDA(ctx, cudaMemcpyAsync(&count, counters.p + 2, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 		Y4_CUDA(ctx, cudaStreamSynchronize(st));
 		uint32_t *t = cur; cur = nxt; nxt = t;
 		ctx->stats.kernel_launches++;
 		if(++levels > 256) { ctx->err = "collapse did not terminate"; return Y4GPU_ERR_CUDA; }
 	}
+	res.levels = levels;
+	uint32_t fin[2];
+	Y4_CUDA(ctx, cudaMemcpyAsync(fin, counters.p, sizeof(fin), cudaMemcpyDeviceToHost, st));
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	Y4_CUDA(ctx, cudaGetLastError());
+	if(fin[1] != (uint32_t) n) { ctx->err = "collapse lost triangles"; return Y4GPU_ERR_CUDA; }
+	res.n_nodes = fin[0];
+	// shrink the node array to its final size so only the live BVH stays resident
+	if(res.n_nodes < max_nodes)
+	{
+		Y4U4 *small = nullptr;
+		if(cudaMalloc(&small, res.n_nodes * Y4_NODE_WORDS * sizeof(Y4U4)) == cudaSuccess)
+		{
+			Y4_CUDA(ctx, cudaMemcpyAsync(small, nodes, res.n_nodes * Y4_NODE_WORDS * sizeof(Y4U4), cudaMemcpyDeviceToDevice, st));
+			Y4_CUDA(ctx, cudaStreamSynchronize(st));
+			cudaFree(nodes);
+			res.nodes = small;
+		}
+		else cudaGetLastError();
+	}
+	ctx->stats.kernel_launches += 1;
+	return Y4GPU_OK;
+}
+
+// reference tree bound inflation, accelerator_kdtree.cc:81-85 (double arithmetic, stored as float)
+static void set_bounds(y4gpu_ctx *ctx, const float raw[6])
+{
+	for(int a = 0; a < 6; ++a) ctx->raw_bound[a] = raw[a];
+	for(int a = 0; a < 3; ++a)
+	{
+		const double foo = (double) (ctx->raw_bound[3 + a] - ctx->raw_bound[a]) * 0.001;
+		ctx->bound[a] = (float) ((double) ctx->raw_bound[a] - foo);
+		ctx->bound[3 + a] = (float) ((double) ctx->raw_bound[3 + a] + foo);
+	}
+}
+
+int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max)
+{
+	const int n = (int) ctx->n_tri;
+	cudaStream_t st = ctx->stream;
+	y4_free_two_level(ctx);
+	if(ctx->d_nodes) { cudaFree(ctx->d_nodes); ctx->d_nodes = nullptr; }
+	if(ctx->d_tris) { cudaFree(ctx->d_tris); ctx->d_tris = nullptr; }
+	ctx->n_nodes = 0;
+	for(int k = 0; k < 6; ++k) ctx->raw_bound[k] = ctx->bound[k] = 0.f;
+	if(n == 0) { ctx->built = true; return Y4GPU_OK; }
+	if(leaf_max < 1 || leaf_max > 3) { ctx->err = "leaf_max must be 1..3"; return Y4GPU_ERR_ARG; }
+	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+	Y4Built b;
+	const int rc = build_core(ctx, ctx->d_verts, ctx->d_flags, n, leaf_max, b);
+	ctx->d_nodes = b.nodes; ctx->d_tris = b.tris;
+	if(rc) return rc;
+	Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	set_bounds(ctx, b.raw);
+	ctx->morton_used = b.morton_used;
 	// the traversal kernels keep at most one pending sibling group per level plus postponed triangle groups, which are only
 	// pushed while sp < Y4_STACK_SIZE - levels (Y4Bvh8::postpone_sp_limit), on a Y4_STACK_SIZE-entry stack: refuse a tree
 	// they could overflow instead of corrupting memory
-	ctx->bvh_levels = levels;
-	if(levels > Y4_STACK_SIZE - 8)
+	ctx->bvh_levels = b.levels;
+	if(b.levels > Y4_STACK_SIZE - 8)
 	{
 		ctx->err = "BVH8 is deeper than the traversal stack (degenerate input: very many coincident triangles)";
 		return Y4GPU_ERR_UNSUPPORTED;
 	}
-	uint32_t fin[2];
-	Y4_CUDA(ctx, cudaMemcpyAsync(fin, counters.p, sizeof(fin), cudaMemcpyDeviceToHost, st));
+	ctx->n_nodes = b.n_nodes;
+	float ms = 0.f;
+	cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+	ctx->stats.build_ms = ms;
+	ctx->stats.n_tris = n; ctx->stats.n_nodes = ctx->n_nodes; ctx->stats.bvh_levels = (uint64_t) b.levels;
+	ctx->stats.node_bytes = ctx->n_nodes * Y4_NODE_WORDS * sizeof(Y4U4);
+	ctx->stats.tri_bytes = (uint64_t) n * sizeof(Y4Tri);
+	ctx->built = true;
+	return Y4GPU_OK;
+}
+
+// ---- two-level build: one bottom-level BVH8 per base mesh in object space, one top-level BVH8 over the instances ----
+namespace {
+
+// leaf records of a bottom-level tree: replace {v0, eps | e1, prim | e2, flags} by the three object-space vertices (Y4TriObj)
+__global__ void __launch_bounds__(256) k_blas_leaves(Y4Tri *__restrict__ tris, int n, const float *__restrict__ verts)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= n) return;
+	const uint32_t prim = tris[i].prim, flags = tris[i].flags;
+	Y4TriObj o;
+	const float *v = verts + 9ull * prim;
+#pragma unroll
+	for(int k = 0; k < 9; ++k) o.v[k] = v[k];
+	o.prim_local = prim; o.flags = flags; o.pad0 = 0u;
+	*reinterpret_cast<Y4TriObj *>(tris + i) = o;
+}
+
+// exact world box of every instance (all vertices through the reference's Matrix4 * Point3) as a proxy triangle with that box:
+// v0 = lo, v1 = hi, v2 = (lo.x, hi.y, lo.z).  One CTA per instance.
+__global__ void __launch_bounds__(256) k_inst_proxy(const Y4Inst *__restrict__ inst, const float *__restrict__ mesh_verts,
+                                                    const unsigned long long *__restrict__ mesh_first, float *__restrict__ proxy)
+{
+	const Y4Inst in = inst[blockIdx.x];
+	const float *v = mesh_verts + 9ull * mesh_first[in.mesh];
+	float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+	for(uint32_t k = threadIdx.x; k < 3u * in.n_tri; k += blockDim.x)
+	{
+		V3 p = v3(v[3 * k], v[3 * k + 1], v[3 * k + 2]);
+		if(!in.identity) p = y4_inst_point(in.m, p);
+		lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
+		hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
+	}
+	__shared__ float s_lo[3][8], s_hi[3][8];
+#pragma unroll
+	for(int a = 0; a < 3; ++a)
+	{
+#pragma unroll
+		for(int o = 16; o > 0; o >>= 1) { lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o)); hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o)); }
+		if((threadIdx.x & 31) == 0) { s_lo[a][threadIdx.x >> 5] = lo[a]; s_hi[a][threadIdx.x >> 5] = hi[a]; }
+	}
+	__syncthreads();
+	if(threadIdx.x == 0)
+	{
+		for(int a = 0; a < 3; ++a) for(int w = 1; w < 8; ++w) { s_lo[a][0] = fminf(s_lo[a][0], s_lo[a][w]); s_hi[a][0] = fmaxf(s_hi[a][0], s_hi[a][w]); }
+		float *q = proxy + 9ull * blockIdx.x;
+		q[0] = s_lo[0][0]; q[1] = s_lo[1][0]; q[2] = s_lo[2][0]; q[3] = s_hi[0][0]; q[4] = s_hi[1][0]; q[5] = s_hi[2][0];
+		q[6] = s_lo[0][0]; q[7] = s_hi[1][0]; q[8] = s_lo[2][0];
+	}
+}
+
+// inverse of the affine map [A | t] in double, rounded to float
+void inverse_affine(const float *m, float *mi)
+{
+	const double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+	const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+	const double id = 1.0 / det;
+	const double r[9] = {(e * i - f * h) * id, (c * h - b * i) * id, (b * f - c * e) * id,
+	                     (f * g - d * i) * id, (a * i - c * g) * id, (c * d - a * f) * id,
+	                     (d * h - e * g) * id, (b * g - a * h) * id, (a * e - b * d) * id};
+	for(int k = 0; k < 3; ++k)
+	{
+		mi[4 * k] = (float) r[3 * k]; mi[4 * k + 1] = (float) r[3 * k + 1]; mi[4 * k + 2] = (float) r[3 * k + 2];
+		mi[4 * k + 3] = (float) -(r[3 * k] * (double) m[3] + r[3 * k + 1] * (double) m[7] + r[3 * k + 2] * (double) m[11]);
+	}
+}
+
+} // namespace
+
+void y4_free_two_level(y4gpu_ctx *ctx)
+{
+	cudaFree(ctx->d_inst); cudaFree(ctx->d_tlas_nodes); cudaFree(ctx->d_tlas_leaves); cudaFree(ctx->d_blas_nodes); cudaFree(ctx->d_blas_tris);
+	ctx->d_inst = nullptr; ctx->d_tlas_nodes = nullptr; ctx->d_tlas_leaves = nullptr; ctx->d_blas_nodes = nullptr; ctx->d_blas_tris = nullptr;
+	ctx->n_tlas_nodes = ctx->n_blas_nodes = 0;
+}
+
+int y4_build_two_level(y4gpu_ctx *ctx, int leaf_max)
+{
+	cudaStream_t st = ctx->stream;
+	y4_free_two_level(ctx);
+	if(ctx->d_nodes) { cudaFree(ctx->d_nodes); ctx->d_nodes = nullptr; }
+	if(ctx->d_tris) { cudaFree(ctx->d_tris); ctx->d_tris = nullptr; }
+	ctx->n_nodes = 0;
+	for(int k = 0; k < 6; ++k) ctx->raw_bound[k] = ctx->bound[k] = 0.f;
+	const size_t n_mesh = ctx->mesh_first.empty() ? 0 : ctx->mesh_first.size() - 1, n_inst = ctx->h_inst.size();
+	if(n_inst == 0 || ctx->n_tri == 0) { ctx->built = true; return Y4GPU_OK; }
+	if(leaf_max < 1 || leaf_max > 3) { ctx->err = "leaf_max must be 1..3"; return Y4GPU_ERR_ARG; }
+	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+	// bottom level: every mesh on its own, then pooled (node / leaf indices stay mesh-relative: the instance carries the offsets)
+	std::vector<Y4Built> blas(n_mesh);
+	std::vector<uint32_t> node_off(n_mesh, 0u), tri_off(n_mesh, 0u);
+	std::vector<float> bmax(n_mesh, 0.f);
+	uint64_t nodes_total = 0, tris_total = 0;
+	int blas_levels = 0, rc = Y4GPU_OK;
+	for(size_t i = 0; i < n_mesh && !rc; ++i)
+	{
+		const uint64_t first = ctx->mesh_first[i], n = ctx->mesh_first[i + 1] - first;
+		if(n == 0) continue;
+		rc = build_core(ctx, ctx->d_mesh_verts + 9ull * first, ctx->d_mesh_flags ? ctx->d_mesh_flags + first : nullptr, (int) n, leaf_max, blas[i]);
+		if(rc) break;
+		k_blas_leaves<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(blas[i].tris, (int) n, ctx->d_mesh_verts + 9ull * first);
+		node_off[i] = (uint32_t) nodes_total; tri_off[i] = (uint32_t) tris_total;
+		nodes_total += blas[i].n_nodes; tris_total += n;
+		if(blas[i].levels > blas_levels) blas_levels = blas[i].levels;
+		for(int k = 0; k < 6; ++k) bmax[i] = fmaxf(bmax[i], fabsf(blas[i].raw[k]));
+	}
+	auto free_blas = [&]() { for(Y4Built &b : blas) { cudaFree(b.nodes); cudaFree(b.tris); b.nodes = nullptr; b.tris = nullptr; } };
+	if(rc) { free_blas(); return rc; }
+	if(cudaMalloc(&ctx->d_blas_nodes, nodes_total * Y4_NODE_WORDS * sizeof(Y4U4)) != cudaSuccess || cudaMalloc(&ctx->d_blas_tris, tris_total * sizeof(Y4TriObj)) != cudaSuccess)
+	{
+		free_blas(); ctx->err = "cudaMalloc of the pooled bottom-level trees failed"; return Y4GPU_ERR_CUDA;
+	}
+	for(size_t i = 0; i < n_mesh; ++i)
+	{
+		const uint64_t n = ctx->mesh_first[i + 1] - ctx->mesh_first[i];
+		if(n == 0) continue;
+		cudaMemcpyAsync(ctx->d_blas_nodes + (size_t) node_off[i] * Y4_NODE_WORDS, blas[i].nodes, blas[i].n_nodes * Y4_NODE_WORDS * sizeof(Y4U4), cudaMemcpyDeviceToDevice, st);
+		cudaMemcpyAsync(ctx->d_blas_tris + tri_off[i], blas[i].tris, n * sizeof(Y4TriObj), cudaMemcpyDeviceToDevice, st);
+	}
+	Y4_CUDA(ctx, cudaStreamSynchronize(st));
+	free_blas();
+	ctx->n_blas_nodes = nodes_total; ctx->n_base_tris = tris_total;
+	// instances: offsets of their mesh, inverse transforms; device copy; exact world boxes as proxy triangles; top-level tree
+	for(Y4Inst &in : ctx->h_inst)
+	{
+		in.node_off = node_off[in.mesh]; in.tri_off = tri_off[in.mesh]; in.bmax = bmax[in.mesh];
+		if(in.identity) { const float id[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0}; memcpy(in.mi, id, sizeof(id)); }
+		else inverse_affine(in.m, in.mi);
+	}
+	Y4_CUDA(ctx, cudaMalloc(&ctx->d_inst, n_inst * sizeof(Y4Inst)));
+	Y4_CUDA(ctx, cudaMemcpyAsync(ctx->d_inst, ctx->h_inst.data(), n_inst * sizeof(Y4Inst), cudaMemcpyHostToDevice, st));
+	DevBuf<float> proxy; DevBuf<unsigned long long> d_first;
+	Y4_CUDA(ctx, proxy.alloc(9 * n_inst)); Y4_CUDA(ctx, d_first.alloc(n_mesh + 1));
+	Y4_CUDA(ctx, cudaMemcpyAsync(d_first.p, ctx->mesh_first.data(), (n_mesh + 1) * sizeof(unsigned long long), cudaMemcpyHostToDevice, st));
+	k_inst_proxy<<<(unsigned) n_inst, 256, 0, st>>>(ctx->d_inst, ctx->d_mesh_verts, d_first.p, proxy.p);
+	Y4Built top;
+	rc = build_core(ctx, proxy.p, nullptr, (int) n_inst, leaf_max, top);
+	ctx->d_tlas_nodes = top.nodes; ctx->d_tlas_leaves = top.tris;
+	if(rc) return rc;
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
 	Y4_CUDA(ctx, cudaStreamSynchronize(st));
 	Y4_CUDA(ctx, cudaGetLastError());
-	if(fin[1] != (uint32_t) n) { ctx->err = "collapse lost triangles"; return Y4GPU_ERR_CUDA; }
-	ctx->n_nodes = fin[0];
-	// shrink the node array to its final size so only the live BVH stays resident
-	if(ctx->n_nodes < max_nodes)
+	ctx->n_tlas_nodes = top.n_nodes;
+	set_bounds(ctx, top.raw);            // the union of the instances' exact world boxes = the flattened scene's bound
+	ctx->bvh_levels = top.levels + blas_levels;
+	// stack: one pending group per level of either tree, plus per instance entry a pending node group, a pending leaf group and the marker
+	if(top.levels + blas_levels + 3 > Y4_STACK_SIZE - 8)
 	{
-		Y4U4 *small = nullptr;
-		if(cudaMalloc(&small, ctx->n_nodes * Y4_NODE_WORDS * sizeof(Y4U4)) == cudaSuccess)
-		{
-			Y4_CUDA(ctx, cudaMemcpyAsync(small, nodes, ctx->n_nodes * Y4_NODE_WORDS * sizeof(Y4U4), cudaMemcpyDeviceToDevice, st));
-			Y4_CUDA(ctx, cudaStreamSynchronize(st));
-			cudaFree(nodes);
-			ctx->d_nodes = small;
-		}
-		else cudaGetLastError();
+		ctx->err = "two-level BVH8 is deeper than the traversal stack";
+		return Y4GPU_ERR_UNSUPPORTED;
 	}
 	float ms = 0.f;
 	cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
 	ctx->stats.build_ms = ms;
-	ctx->stats.n_tris = n; ctx->stats.n_nodes = ctx->n_nodes; ctx->stats.bvh_levels = (uint64_t) levels;
-	ctx->stats.node_bytes = ctx->n_nodes * Y4_NODE_WORDS * sizeof(Y4U4);
-	ctx->stats.tri_bytes = (uint64_t) n * sizeof(Y4Tri);
-	ctx->stats.kernel_launches += 1;
+	ctx->stats.n_tris = ctx->n_tri; ctx->stats.n_nodes = nodes_total + top.n_nodes; ctx->stats.bvh_levels = (uint64_t) ctx->bvh_levels;
+	ctx->stats.node_bytes = (nodes_total + top.n_nodes) * Y4_NODE_WORDS * sizeof(Y4U4);
+	ctx->stats.tri_bytes = tris_total * sizeof(Y4TriObj) + n_inst * (sizeof(Y4Tri) + sizeof(Y4Inst));
+	ctx->stats.kernel_launches += n_mesh + 1;
 	ctx->built = true;
 	return Y4GPU_OK;
 }

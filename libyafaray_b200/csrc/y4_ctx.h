@@ -52,6 +52,17 @@ struct y4gpu_ctx
 	float raw_bound[6] = {0, 0, 0, 0, 0, 0};
 	float bound[6] = {0, 0, 0, 0, 0, 0};
 
+	// two-level scene (y4gpu_upload_instanced): base meshes in object space + instances; n_tri is then the number of instanced
+	// triangles (the primitive index space), d_verts / d_flags / d_nodes / d_tris stay empty
+	bool two_level = false;
+	float *d_mesh_verts = nullptr; uint32_t *d_mesh_flags = nullptr;      // all meshes, concatenated
+	std::vector<uint64_t> mesh_first;                                      // [n_mesh + 1] first triangle of mesh i in the concatenation
+	std::vector<Y4Inst> h_inst;                                            // as uploaded (node_off / tri_off / bmax filled by the build)
+	Y4Inst *d_inst = nullptr;
+	Y4U4 *d_tlas_nodes = nullptr; Y4Tri *d_tlas_leaves = nullptr;
+	Y4U4 *d_blas_nodes = nullptr; Y4TriObj *d_blas_tris = nullptr;
+	uint64_t n_tlas_nodes = 0, n_blas_nodes = 0, n_base_tris = 0;
+
 	// staging for host-pointer batches and work counters
 	Y4Ray *d_rays = nullptr;
 	void *d_hits = nullptr;
@@ -85,6 +96,11 @@ struct y4gpu_ctx
 	std::vector<Y4TraceSlot *> free_slots, all_slots;
 	Y4Pt *pt = nullptr;
 
+	Y4Scene2 view2() const
+	{
+		Y4Scene2 v; v.tlas_nodes = d_tlas_nodes; v.tlas_leaves = d_tlas_leaves; v.inst = d_inst; v.n_inst = (uint32_t) h_inst.size();
+		v.blas_nodes = d_blas_nodes; v.blas_tris = d_blas_tris; v.consts = d_consts; return v;
+	}
 	Y4Bvh8 view() const { Y4Bvh8 v; v.nodes = d_nodes; v.tris = d_tris; v.n_tris = (uint32_t) n_tri; v.consts = d_consts; v.postpone_sp_limit = Y4_STACK_SIZE - bvh_levels; return v; }
 };
 
@@ -100,6 +116,8 @@ struct y4gpu_ctx
 
 // y4_build.cu
 int y4_build_bvh(y4gpu_ctx *ctx, int leaf_max);
+int y4_build_two_level(y4gpu_ctx *ctx, int leaf_max);       // after y4gpu_upload_instanced
+void y4_free_two_level(y4gpu_ctx *ctx);                     // the built two-level structures (not the uploaded meshes)
 // y4_trace.cu
 int y4_launch_trace(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays, uint64_t n, Y4Hit *d_out);
 int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_rays, Y4Hit *d_out, uint64_t n_max,

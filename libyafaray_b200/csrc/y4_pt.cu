@@ -302,6 +302,29 @@ __global__ void __launch_bounds__(kCompactThreads, MINB) k_pt_path_compact(const
 	}
 }
 
+// the same record for a two-level scene: the instance that owns the primitive (binary search over first_prim), its triangle's
+// object-space vertices through the reference's Matrix4 * Point3 -- the vertices the flattened scene would hold
+__global__ void __launch_bounds__(kPtThreads) k_pt_tri_shade2(const Y4Inst *__restrict__ inst, uint32_t n_inst, const float *__restrict__ mesh_verts,
+                                                              const uint32_t *__restrict__ mesh_flags, uint32_t n_mats, uint64_t n_tri, float4 *__restrict__ out)
+{
+	for(uint64_t t = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x; t < n_tri; t += (uint64_t) gridDim.x * blockDim.x)
+	{
+		uint32_t lo = 0u, hi = n_inst - 1u;
+		while(lo < hi) { const uint32_t mid = (lo + hi + 1u) >> 1; if(inst[mid].first_prim <= (uint32_t) t) lo = mid; else hi = mid - 1u; }
+		const Y4Inst &in = inst[lo];
+		const uint64_t base = (uint64_t) in.vert_first + ((uint32_t) t - in.first_prim);
+		const float *v = mesh_verts + 9ull * base;
+		V3 a = v3(v[0], v[1], v[2]), b = v3(v[3], v[4], v[5]), c = v3(v[6], v[7], v[8]);
+		if(!in.identity) { a = y4_inst_point(in.m, a); b = y4_inst_point(in.m, b); c = y4_inst_point(in.m, c); }
+		const float w[9] = {a.x, a.y, a.z, b.x, b.y, b.z, c.x, c.y, c.z};
+		float4 r = y4_tri_shade(w, nullptr, n_mats, 0);
+		uint32_t mat = mesh_flags ? (mesh_flags[base] >> Y4_TRI_MAT_SHIFT) : 0u;
+		if(mat >= n_mats) mat = 0u;
+		r.w = y4_u2f(mat);
+		out[t] = r;
+	}
+}
+
 __global__ void __launch_bounds__(kPtThreads) k_pt_tri_shade(const float *__restrict__ verts, const uint32_t *__restrict__ tri_flags, uint32_t n_mats, uint64_t n_tri, float4 *__restrict__ out)
 {
 	for(uint64_t t = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x; t < n_tri; t += (uint64_t) gridDim.x * blockDim.x) out[t] = y4_tri_shade(verts, tri_flags, n_mats, t);
@@ -710,7 +733,8 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	{
 		if(!pt->d_tri_shade) { Y4_CUDA(ctx, cudaMalloc(&pt->d_tri_shade, ctx->n_tri * sizeof(float4))); pt->tri_cap = ctx->n_tri; }
 		const uint64_t want = (ctx->n_tri + kPtThreads - 1) / kPtThreads, full = (uint64_t) ctx->sm_count * 8u;
-		k_pt_tri_shade<<<(int) (want < full ? want : full), kPtThreads, 0, st>>>(ctx->d_verts, ctx->d_flags, n_mat, ctx->n_tri, pt->d_tri_shade);
+		if(ctx->two_level) k_pt_tri_shade2<<<(int) (want < full ? want : full), kPtThreads, 0, st>>>(ctx->d_inst, (uint32_t) ctx->h_inst.size(), ctx->d_mesh_verts, ctx->d_mesh_flags, n_mat, ctx->n_tri, pt->d_tri_shade);
+		else k_pt_tri_shade<<<(int) (want < full ? want : full), kPtThreads, 0, st>>>(ctx->d_verts, ctx->d_flags, n_mat, ctx->n_tri, pt->d_tri_shade);
 		Y4_CUDA(ctx, cudaGetLastError());
 	}
 	sc.lights = pt->d_lights; sc.mats = pt->d_mats; sc.tri_shade = pt->d_tri_shade; sc.normals = pt->d_normals;

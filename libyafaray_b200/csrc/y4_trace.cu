@@ -231,6 +231,36 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow_queue(Y4Bvh8 bv
 	}
 }
 
+// Two-level scenes (y4_trace_ray2): persistent warps take packets of 32 rays (or queue entries) and every lane walks its ray
+// to the end.  Same batch conventions as k_trace.
+template<int KIND, bool QUEUE>
+__global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const Y4Ray *__restrict__ rays, uint64_t n, Y4Hit *__restrict__ out,
+                                                             unsigned long long *__restrict__ work_counter,
+                                                             const uint32_t *__restrict__ queue, const uint32_t *__restrict__ queue_count)
+{
+	if(QUEUE) n = __ldg(queue_count);
+	const uint32_t lane = threadIdx.x & 31u;
+	uint2 stack[Y4_STACK_SIZE];
+	while(true)
+	{
+		unsigned long long base = 0;
+		if(lane == 0) base = atomicAdd(work_counter, 32ull);
+		base = __shfl_sync(0xffffffffu, base, 0);
+		if(base >= n) break;
+		const uint64_t mine = base + lane;
+		if(mine >= n) continue;
+		const uint64_t slot_i = (QUEUE && queue) ? (uint64_t) __ldg(queue + mine) : mine;
+		const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + slot_i));
+		const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + slot_i) + 1);
+		Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
+		const Y4PreparedRay pr = y4_prepare_ray(r, KIND);
+		Y4Hit hit;
+		y4_trace_ray2<KIND>(sc, pr, hit, stack, nullptr);
+		float4 o; o.x = hit.t; o.y = hit.bu; o.z = hit.bv; o.w = __int_as_float(hit.prim);
+		*reinterpret_cast<float4 *>(out + slot_i) = o;
+	}
+}
+
 struct TraceArgs
 {
 	const Y4Ray *rays; uint64_t n; Y4Hit *out;
@@ -260,8 +290,25 @@ int launch_k(y4gpu_ctx *ctx, const TraceArgs &a)
 	return Y4GPU_OK;
 }
 template<int KIND, bool QUEUE>
+int launch2(y4gpu_ctx *ctx, const TraceArgs &a)
+{
+	static int per_sm_cached[16] = {0};
+	int &per_sm = per_sm_cached[ctx->device & 15];
+	if(per_sm < 1)
+	{
+		Y4_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace2<KIND, QUEUE>, kTraceThreads, 0));
+		if(per_sm < 1) per_sm = 1;
+	}
+	const uint64_t want = (a.n + kTraceThreads - 1) / kTraceThreads;
+	const int use_per_sm = (a.max_blocks_per_sm > 0 && a.max_blocks_per_sm < per_sm) ? a.max_blocks_per_sm : per_sm;
+	const uint64_t full = (uint64_t) ctx->sm_count * use_per_sm;
+	k_trace2<KIND, QUEUE><<<(int) (want < full ? want : full), kTraceThreads, 0, a.stream>>>(ctx->view2(), a.rays, a.n, a.out, a.work_counter, a.queue, a.queue_count);
+	return Y4GPU_OK;
+}
+template<int KIND, bool QUEUE>
 int launch(y4gpu_ctx *ctx, bool counted, const TraceArgs &a)
 {
+	if(ctx->two_level) return launch2<KIND, QUEUE>(ctx, a);        // (no visit counters in the two-level kernel)
 	if(counted) return launch_k<KIND, true, 3, QUEUE>(ctx, a);
 	return ctx->min_blocks >= 4 ? launch_k<KIND, false, 4, QUEUE>(ctx, a) : launch_k<KIND, false, 3, QUEUE>(ctx, a);
 }
@@ -347,7 +394,7 @@ int y4_ray_sort_wanted(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, Y4SortSc
 	want = false;
 	if(ctx->ray_sort == 0 || n < (1u << 16) || n >= (1ull << 31)) return Y4GPU_OK;
 	if(ctx->ray_sort == 1) { want = true; return Y4GPU_OK; }
-	if((ctx->n_nodes * 80ull + ctx->n_tri * 48ull) < ctx->ray_sort_min_bvh_bytes) return Y4GPU_OK;
+	if((ctx->stats.node_bytes + ctx->stats.tri_bytes) < ctx->ray_sort_min_bvh_bytes) return Y4GPU_OK;
 	const int rc = y4_sort_scratch_reserve(ctx, sc, n);
 	if(rc) return rc;
 	unsigned long long *d_sum = reinterpret_cast<unsigned long long *>(static_cast<char *>(sc.buf) + (size_t) n * 16 + 8);
@@ -452,6 +499,7 @@ int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_
 int y4_launch_tshadow_wave(y4gpu_ctx *ctx, const Y4Ray *d_rays, Y4Hit *d_out, const uint32_t *d_queue, const uint32_t *d_queue_count, int max_depth,
                            const float *d_mat_transp, uint32_t n_mat, unsigned long long *d_work_counter, cudaStream_t stream, int max_blocks_per_sm)
 {
+	if(ctx->two_level) { ctx->err = "filtered transparent shadows are not available on a two-level (instanced) scene"; return Y4GPU_ERR_UNSUPPORTED; }
 	const int per_sm = max_blocks_per_sm > 0 && max_blocks_per_sm < 4 ? max_blocks_per_sm : 4;
 	k_trace_tshadow_queue<<<ctx->sm_count * per_sm, kTraceThreads, 0, stream>>>(ctx->view(), d_rays, d_queue, d_queue_count, max_depth, d_mat_transp, n_mat, d_out, d_work_counter);
 	Y4_CUDA(ctx, cudaGetLastError());
@@ -461,6 +509,7 @@ int y4_launch_tshadow_wave(y4gpu_ctx *ctx, const Y4Ray *d_rays, Y4Hit *d_out, co
 
 int y4_launch_tshadow(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out)
 {
+	if(ctx->two_level) { ctx->err = "filtered transparent shadows are not available on a two-level (instanced) scene"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(n == 0) return Y4GPU_OK;
 	cudaStream_t st = ctx->stream;
 	Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_work_counter, 0, sizeof(uint32_t), st));
@@ -493,6 +542,7 @@ int y4_launch_trace_on(y4gpu_ctx *ctx, int kind, const Y4Ray *d_rays, uint64_t n
 int y4_launch_tshadow_on(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out,
                          bool inner, unsigned long long *d_work_counter, cudaStream_t stream)
 {
+	if(ctx->two_level) { ctx->err = "filtered transparent shadows are not available on a two-level (instanced) scene"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(n == 0) return Y4GPU_OK;
 	const uint64_t want = (n + kTraceThreads - 1) / kTraceThreads;
 	const uint64_t full = (uint64_t) ctx->sm_count * 4;

@@ -4,6 +4,7 @@
 // Never linked into liby4gpu.so; the product path has no CPU fallback.
 #include "../../libyafaray_b200/csrc/y4_trace.cuh"
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -105,6 +106,96 @@ int emu_build_trace(const float *verts, const uint32_t *flags, int n, const floa
 	}
 	if(stats_out) { stats_out[0] = sn; stats_out[1] = st; }
 	return (int) b.n_nodes;
+}
+
+// Two-level scene: `n_mesh` base meshes in object space (vertices concatenated, mesh_tris[i] triangles each),
+// `n_inst` instances {mesh, identity, 12 matrix floats (rows of Matrix4)} in primitive order.  Builds a bottom-level BVH8 per
+// mesh and a top-level BVH8 over the instances' exact world boxes (the product does the same in y4_build.cu) and traces.
+void emu_inverse_affine(const float *m, float *mi)
+{
+	const double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+	const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+	const double id = 1.0 / det;
+	const double r[9] = {(e * i - f * h) * id, (c * h - b * i) * id, (b * f - c * e) * id,
+	                     (f * g - d * i) * id, (a * i - c * g) * id, (c * d - a * f) * id,
+	                     (d * h - e * g) * id, (b * g - a * h) * id, (a * e - b * d) * id};
+	for(int k = 0; k < 3; ++k)
+	{
+		mi[4 * k] = (float) r[3 * k]; mi[4 * k + 1] = (float) r[3 * k + 1]; mi[4 * k + 2] = (float) r[3 * k + 2];
+		mi[4 * k + 3] = (float) -(r[3 * k] * (double) m[3] + r[3 * k + 1] * (double) m[7] + r[3 * k + 2] * (double) m[11]);
+	}
+}
+
+int emu_build_trace2(const float *mesh_verts, const uint32_t *mesh_flags, const int *mesh_tris, int n_mesh,
+                     const int *inst_mesh, const int *inst_identity, const float *inst_matrix, int n_inst,
+                     const float *rays, int m, int kind, Y4Hit *hits, uint64_t *stats_out)
+{
+	std::vector<size_t> mesh_first(n_mesh + 1, 0);
+	for(int i = 0; i < n_mesh; ++i) mesh_first[i + 1] = mesh_first[i] + (size_t) mesh_tris[i];
+	// bottom level
+	std::vector<Y4U4> blas_nodes; std::vector<Y4TriObj> blas_tris;
+	std::vector<uint32_t> node_off(n_mesh), tri_off(n_mesh);
+	std::vector<float> bmax(n_mesh, 0.f);
+	for(int i = 0; i < n_mesh; ++i)
+	{
+		const float *v = mesh_verts + 9 * mesh_first[i];
+		const uint32_t *f = mesh_flags ? mesh_flags + mesh_first[i] : nullptr;
+		EmuBvh b;
+		emu_build(v, f, mesh_tris[i], 3, b);
+		node_off[i] = (uint32_t) (blas_nodes.size() / Y4_NODE_WORDS); tri_off[i] = (uint32_t) blas_tris.size();
+		blas_nodes.insert(blas_nodes.end(), b.nodes.begin(), b.nodes.begin() + (size_t) b.n_nodes * Y4_NODE_WORDS);
+		for(const Y4Tri &t : b.tris)
+		{
+			Y4TriObj o; memcpy(o.v, v + 9ull * t.prim, 36); o.prim_local = t.prim; o.flags = t.flags; o.pad0 = 0u;
+			blas_tris.push_back(o);
+		}
+		for(size_t k = 0; k < 9 * (size_t) mesh_tris[i]; ++k) bmax[i] = std::max(bmax[i], std::fabs(v[k]));
+	}
+	// instances + their exact world boxes as proxy triangles (v0 = lo, v1 = hi, v2 = (lo.x, hi.y, lo.z): the same box)
+	std::vector<Y4Inst> inst(n_inst);
+	std::vector<float> proxy(9 * (size_t) n_inst);
+	uint32_t first_prim = 0;
+	for(int i = 0; i < n_inst; ++i)
+	{
+		Y4Inst &in = inst[i];
+		memset(&in, 0, sizeof(in));
+		memcpy(in.m, inst_matrix + 12 * i, 48);
+		emu_inverse_affine(in.m, in.mi);
+		const int me = inst_mesh[i];
+		in.node_off = node_off[me]; in.tri_off = tri_off[me]; in.first_prim = first_prim; in.identity = inst_identity[i] ? 1u : 0u;
+		in.bmax = bmax[me]; in.n_tri = (uint32_t) mesh_tris[me]; in.mesh = (uint32_t) me; in.vert_first = (uint32_t) mesh_first[me];
+		first_prim += in.n_tri;
+		Y4Box wb = y4_box_empty();
+		const float *v = mesh_verts + 9 * mesh_first[me];
+		for(size_t k = 0; k < 3 * (size_t) mesh_tris[me]; ++k)
+		{
+			V3 p = v3(v[3 * k], v[3 * k + 1], v[3 * k + 2]);
+			if(!in.identity) p = y4_inst_point(in.m, p);
+			wb.lox = fminf(wb.lox, p.x); wb.loy = fminf(wb.loy, p.y); wb.loz = fminf(wb.loz, p.z);
+			wb.hix = fmaxf(wb.hix, p.x); wb.hiy = fmaxf(wb.hiy, p.y); wb.hiz = fmaxf(wb.hiz, p.z);
+		}
+		float *q = proxy.data() + 9ull * i;
+		q[0] = wb.lox; q[1] = wb.loy; q[2] = wb.loz; q[3] = wb.hix; q[4] = wb.hiy; q[5] = wb.hiz; q[6] = wb.lox; q[7] = wb.hiy; q[8] = wb.loz;
+	}
+	EmuBvh top;
+	emu_build(proxy.data(), nullptr, n_inst, 3, top);
+	Y4Scene2 sc;
+	sc.tlas_nodes = top.nodes.data(); sc.tlas_leaves = top.tris.data(); sc.inst = inst.data(); sc.n_inst = (uint32_t) n_inst;
+	sc.blas_nodes = blas_nodes.data(); sc.blas_tris = blas_tris.data(); sc.consts = nullptr;
+	uint64_t sn = 0, st = 0;
+	for(int i = 0; i < m; ++i)
+	{
+		Y4Ray r; memcpy(&r, rays + 8ull * i, sizeof(r));
+		const Y4PreparedRay pr = y4_prepare_ray(r, kind);
+		uint2 stack[Y4_STACK_SIZE];
+		Y4TraceStats s{0, 0};
+		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray2<Y4_TRACE_CLOSEST>(sc, pr, hits[i], stack, &s);
+		else if(kind == Y4_TRACE_SHADOW) y4_trace_ray2<Y4_TRACE_SHADOW>(sc, pr, hits[i], stack, &s);
+		else y4_trace_ray2<Y4_TRACE_TSHADOW>(sc, pr, hits[i], stack, &s);
+		sn += s.nodes; st += s.tris;
+	}
+	if(stats_out) { stats_out[0] = sn; stats_out[1] = st; }
+	return (int) (top.n_nodes + blas_nodes.size() / Y4_NODE_WORDS);
 }
 
 // Brute force over all triangles in primitive order with the same exact triangle test.

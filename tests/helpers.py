@@ -57,6 +57,67 @@ def emu_build_trace(tris, rays, kind, leaf_max=1, flags=None):
     return hits, n_nodes, stats
 
 
+def flatten_instances(meshes, instances):
+    """World-space triangles of an instanced scene in primitive order, with the reference's Matrix4 * Point3 arithmetic
+    (fp32, ((m0 x + m1 y) + m2 z) + m3; matrix4.h:85-90) -- what PrimitiveInstance applies per test.
+    meshes: list of [n, 9] fp32 arrays; instances: list of (mesh index, 3x4 matrix or None for a plain object)."""
+    out = []
+    for mesh, mat in instances:
+        v = np.ascontiguousarray(meshes[mesh], np.float32).reshape(-1, 3)
+        if mat is not None:
+            m = np.asarray(mat, np.float32).reshape(3, 4)
+            v = np.stack([((m[r, 0] * v[:, 0] + m[r, 1] * v[:, 1]) + m[r, 2] * v[:, 2]) + m[r, 3] for r in range(3)], -1).astype(np.float32)
+        out.append(v.reshape(-1, 9))
+    return np.ascontiguousarray(np.concatenate(out), np.float32)
+
+
+def mini_city(n_mesh=4, n_inst=40, tris_per_mesh=600, seed=5):
+    """A small instanced scene for the two-level tests: `n_mesh` building meshes (scenes_pt._building) placed `n_inst` times with
+    random yaw / scale / position like scenes_pt.city, plus a plain ground quad.  -> (meshes, instances)."""
+    from libyafaray_b200 import scenes_pt
+    rng = np.random.default_rng(seed)
+    meshes = []
+    for b in range(n_mesh):
+        v, t = scenes_pt._building(0xC4, b, tris_per_mesh)
+        meshes.append(np.asarray(v, np.float64).astype(np.float32)[np.asarray(t, np.int64)].reshape(-1, 9))
+    meshes.append(np.asarray([[-2, 0, -2, -2, 0, 14, 14, 0, 14], [-2, 0, -2, 14, 0, 14, 14, 0, -2]], np.float32))
+    inst = [(n_mesh, None)]
+    for _ in range(n_inst):
+        yaw, sc = rng.uniform(0, 2 * np.pi), rng.uniform(0.55, 0.9)
+        cx, cz = rng.uniform(0, 12, 2)
+        c, s = np.cos(yaw) * sc, np.sin(yaw) * sc
+        inst.append((int(rng.integers(0, n_mesh)), [c, 0, s, cx, 0, sc, 0, 0, -s, 0, c, cz]))
+    return meshes, inst
+
+
+def city_rays(n, seed=6, origin_scale=1.0):
+    """Rays aimed at points inside the mini city from origins `origin_scale` away (far origins stress the object-space padding)."""
+    rng = np.random.default_rng(seed)
+    tgt = np.stack([rng.uniform(0, 12, n), rng.uniform(0, 3, n), rng.uniform(0, 12, n)], -1)
+    o = tgt + rng.normal(size=(n, 3)) * origin_scale
+    d = tgt - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, 0:3], rays[:, 3], rays[:, 4:7], rays[:, 7] = o, 1e-4, d, -1
+    return rays
+
+
+def emu_build_trace2(meshes, instances, rays, kind, mesh_flags=None):
+    """Two-level emulation (tests/emu/emu_bvh.cpp: emu_build_trace2): bottom-level trees per mesh, top level over instances."""
+    mv = np.ascontiguousarray(np.concatenate([np.asarray(m, np.float32).reshape(-1, 9) for m in meshes]), np.float32)
+    mt = np.asarray([len(np.asarray(m).reshape(-1, 9)) for m in meshes], np.int32)
+    mf = None if mesh_flags is None else np.ascontiguousarray(np.concatenate(mesh_flags), np.uint32)
+    im = np.asarray([i[0] for i in instances], np.int32)
+    ii = np.asarray([1 if i[1] is None else 0 for i in instances], np.int32)
+    ident = np.asarray([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0], np.float32)
+    mat = np.ascontiguousarray(np.stack([ident if i[1] is None else np.asarray(i[1], np.float32).reshape(12) for i in instances]), np.float32)
+    rays = np.ascontiguousarray(rays, np.float32)
+    hits = np.zeros(len(rays), HIT_DTYPE)
+    stats = np.zeros(2, np.uint64)
+    n_nodes = emu().emu_build_trace2(_p(mv), _p(mf), _p(mt), len(mt), _p(im), _p(ii), _p(mat), len(im), _p(rays), len(rays), kind, _p(hits), _p(stats))
+    return hits, n_nodes, stats
+
+
 def emu_brute(tris, rays, kind, flags=None):
     tris = np.ascontiguousarray(tris, np.float32)
     rays = np.ascontiguousarray(rays, np.float32)

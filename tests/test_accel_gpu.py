@@ -184,6 +184,37 @@ def test_sorted_ray_order_is_bit_identical_and_the_automatic_mode_leaves_camera_
     acc.set_ray_sort(2)
 
 
+def test_two_level_instanced_scene_equals_the_flattened_upload():
+    """y4gpu_upload_instanced: meshes once + instances on the device; closest hits bit-identical to the flattened upload, any-hit
+    same occlusion, resident and host batches, and a fraction of the memory."""
+    import torch
+    from libyafaray_b200.accelerator import AcceleratorB200
+    meshes, inst = helpers.mini_city(n_mesh=6, n_inst=300, tris_per_mesh=1500)
+    flat = helpers.flatten_instances(meshes, inst)
+    a_flat = AcceleratorB200(flat, leaf_max=3)
+    a_two = AcceleratorB200.from_instances(meshes, inst, leaf_max=3)
+    assert a_two.n_primitives == len(flat)
+    assert np.array_equal(a_flat.getBound(), a_two.getBound())
+    s1, s2 = a_flat.stats(), a_two.stats()
+    assert (s2["node_bytes"] + s2["tri_bytes"]) * 8 < s1["node_bytes"] + s1["tri_bytes"], (s1, s2)
+    for scale, n in ((1.0, 200000), (300.0, 50000)):
+        rays = helpers.city_rays(n, origin_scale=scale)
+        h1, h2 = a_flat.intersect(rays), a_two.intersect(rays)
+        assert np.array_equal(h1.view(np.uint32), h2.view(np.uint32)), int((h1["prim"] != h2["prim"]).sum())
+        assert (h1["prim"] >= 0).mean() > 0.5
+        assert np.array_equal(a_flat.isShadowed(rays)["prim"] >= 0, a_two.isShadowed(rays)["prim"] >= 0)
+        d_rays = torch.from_numpy(rays).cuda()
+        d_out = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+        a_two.intersect(d_rays, d_out)
+        a_two.synchronize()
+        assert np.array_equal(d_out.cpu().numpy().view(np.uint32).reshape(-1), h1.view(np.uint32).reshape(-1))
+    with pytest.raises(Exception):
+        a_two.isShadowedTransparent(rays[:16], 4, np.ones((1, 3), np.float32))      # filtered shadows: flat scenes only
+    # back to a flat scene in the same context
+    a_two.rebuild(flat[:1000])
+    assert np.array_equal(a_two.intersect(rays[:1000]).view(np.uint32), AcceleratorB200(flat[:1000]).intersect(rays[:1000]).view(np.uint32))
+
+
 def test_full_size_c3_properties_and_tree_independence(monkeypatch):
     """BASELINE config C3 at full size (1 M-triangle sphere, 4 Mi + 4 Mi rays here): size-independent properties.
     * a segment is occluded (any-hit) exactly when the closest-hit query over the same range finds something;

@@ -112,3 +112,21 @@ def test_visibility_flags_and_ranges():
     r3 = np.array([[0, -0.5, 5, 1.0, 0, 0, -1, 5.5], [0, -0.5, 5, 1.0, 0, 0, -1, 6.5]], np.float32)
     got = helpers.emu_brute(tris, r3, 1)
     assert list(got["prim"] >= 0) == [False, True]
+
+
+def test_two_level_traversal_equals_the_flattened_scene_bit_for_bit():
+    """base meshes kept once in object space + instances (top-level BVH8 over instance boxes, bottom-level BVH8 per mesh,
+    object-space node tests padded by the transform's rounding, exact WORLD-space triangle test with the reference's per-test
+    vertex transform).  Every hit record equals the one the flattened scene gives, also for rays that start far away."""
+    meshes, inst = helpers.mini_city()
+    flat = helpers.flatten_instances(meshes, inst)
+    for scale, n in ((1.0, 20000), (300.0, 8000)):
+        rays = helpers.city_rays(n, origin_scale=scale)
+        h1, n1, s1 = helpers.emu_build_trace(flat, rays, 0, leaf_max=3)
+        h2, n2, s2 = helpers.emu_build_trace2(meshes, inst, rays, 0)
+        assert np.array_equal(h1.view(np.uint32), h2.view(np.uint32)), int((h1["prim"] != h2["prim"]).sum())
+        assert (h1["prim"] >= 0).mean() > 0.5
+        assert n2 * 5 < n1                       # the instanced structure is a fraction of the flattened tree
+        o1, _, _ = helpers.emu_build_trace(flat, rays, 1, leaf_max=3)
+        o2, _, _ = helpers.emu_build_trace2(meshes, inst, rays, 1)
+        assert np.array_equal(o1["prim"] >= 0, o2["prim"] >= 0)
