@@ -695,7 +695,11 @@ def pt_arm(args, env):
         ye.render_pass(spp_step, 0, 0)
         ye.read_film(pinned=True)
         barrier()
-        h2d = int(ye._assembled["tris"].nbytes + ye._assembled["flags"].nbytes + 4096)
+        asm = ye._assembled
+        if asm.get("two_level"):      # meshes once + one matrix per instance
+            h2d = int(sum(m.nbytes for m in asm["meshes"]) + sum(f.nbytes for f in asm["mesh_flags"]) + 56 * len(asm["instances"]) + 4096)
+        else:
+            h2d = int(asm["tris"].nbytes + asm["flags"].nbytes + 4096)
         t0 = time.perf_counter()
         for k in range(e_steps):
             ye.upload()                                      # host triangles/materials/lights/camera -> device, BVH8 build

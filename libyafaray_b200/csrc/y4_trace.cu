@@ -231,33 +231,137 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow_queue(Y4Bvh8 bv
 	}
 }
 
-// Two-level scenes (y4_trace_ray2): persistent warps take packets of 32 rays (or queue entries) and every lane walks its ray
-// to the end.  Same batch conventions as k_trace.
+// Two-level scenes: the walk of y4_trace_ray2 (y4_trace.cuh) with k_trace's warp scheduling -- lanes whose ray ended are
+// refilled from the work counter as soon as fewer than fetch_threshold lanes are busy.  Per-lane state between steps: the
+// world ray, the current space's ray (world or the instance's object space), the instance index and its tree offsets.
 template<int KIND, bool QUEUE>
 __global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const Y4Ray *__restrict__ rays, uint64_t n, Y4Hit *__restrict__ out,
-                                                             unsigned long long *__restrict__ work_counter,
+                                                             unsigned long long *__restrict__ work_counter, int fetch_threshold,
                                                              const uint32_t *__restrict__ queue, const uint32_t *__restrict__ queue_count)
 {
 	if(QUEUE) n = __ldg(queue_count);
 	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t lt_mask = (1u << lane) - 1u;
+	const uint32_t vis_bit = KIND == Y4_TRACE_CLOSEST ? Y4_TRI_VIS_CLOSEST : (KIND == Y4_TRACE_SHADOW ? Y4_TRI_VIS_SHADOW : Y4_TRI_VIS_TSHADOW);
 	uint2 stack[Y4_STACK_SIZE];
+	bool have = false, exhausted = false;
+	uint64_t ray_i = 0;
+	V3 wo = v3(0.f, 0.f, 0.f), wd = v3(0.f, 0.f, 1.f);
+	Y4RayCtx rc = y4_ray_ctx(wo, wd);
+	float t_lo = 0.f, t_hi = 0.f, pad = 0.f;
+	Y4Hit hit; hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
+	uint2 ngroup; ngroup.x = 0u; ngroup.y = 0u;
+	uint32_t cur = Y4_INST_NONE, node_off = 0u;
+	int sp = 0;
+	const uint32_t magic = __ldg(sc.consts);
 	while(true)
 	{
-		unsigned long long base = 0;
-		if(lane == 0) base = atomicAdd(work_counter, 32ull);
-		base = __shfl_sync(0xffffffffu, base, 0);
-		if(base >= n) break;
-		const uint64_t mine = base + lane;
-		if(mine >= n) continue;
-		const uint64_t slot_i = (QUEUE && queue) ? (uint64_t) __ldg(queue + mine) : mine;
-		const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + slot_i));
-		const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + slot_i) + 1);
-		Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
-		const Y4PreparedRay pr = y4_prepare_ray(r, KIND);
-		Y4Hit hit;
-		y4_trace_ray2<KIND>(sc, pr, hit, stack, nullptr);
-		float4 o; o.x = hit.t; o.y = hit.bu; o.z = hit.bv; o.w = __int_as_float(hit.prim);
-		*reinterpret_cast<float4 *>(out + slot_i) = o;
+		const uint32_t idle = __ballot_sync(0xffffffffu, !have);
+		if(idle && !exhausted)
+		{
+			const uint32_t n_idle = __popc(idle);
+			unsigned long long base = 0;
+			if(lane == 0) base = atomicAdd(work_counter, (unsigned long long) n_idle);
+			base = __shfl_sync(0xffffffffu, base, 0);
+			exhausted = base + n_idle >= n;
+			const uint64_t mine = base + __popc(idle & lt_mask);
+			if(!have && mine < n)
+			{
+				const uint64_t slot_i = (QUEUE && queue) ? (uint64_t) __ldg(queue + mine) : mine;
+				const float4 a = __ldg(reinterpret_cast<const float4 *>(rays + slot_i));
+				const float4 b = __ldg(reinterpret_cast<const float4 *>(rays + slot_i) + 1);
+				Y4Ray r; r.ox = a.x; r.oy = a.y; r.oz = a.z; r.tmin = a.w; r.dx = b.x; r.dy = b.y; r.dz = b.z; r.tmax = b.w;
+				const Y4PreparedRay pr = y4_prepare_ray(r, KIND);
+				wo = pr.o; wd = pr.d;
+				rc = y4_ray_ctx(wo, wd);
+				t_lo = pr.t_lo; t_hi = pr.t_hi; pad = 0.f;
+				hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
+				ray_i = slot_i; sp = 0; have = true; cur = Y4_INST_NONE; node_off = 0u;
+				ngroup.x = 0u; ngroup.y = (sc.n_inst && pr.t_hi > pr.t_lo) ? ((1u << (24u + rc.oct_inv)) | 1u) : 0u;
+			}
+		}
+		if(!__any_sync(0xffffffffu, have)) break;
+		const int leave_below = exhausted ? 0 : fetch_threshold;
+		while(have)
+		{
+			uint2 tgroup; tgroup.x = 0u; tgroup.y = 0u;
+			bool done = false;
+			if(ngroup.y & 0xff000000u)
+			{
+				const uint32_t bit = 31u - (uint32_t) __clz((int) ngroup.y);
+				ngroup.y &= ~(1u << bit);
+				const uint32_t slot = (bit - 24u) ^ rc.oct_inv;
+				const uint32_t child = ngroup.x + __popc(ngroup.y & 0xffu & ((1u << slot) - 1u));
+				if(ngroup.y & 0xff000000u) stack[sp++] = ngroup;
+				const Y4U4 *nd = (cur == Y4_INST_NONE ? sc.tlas_nodes : sc.blas_nodes + (size_t) node_off * Y4_NODE_WORDS) + (size_t) child * Y4_NODE_WORDS;
+				const Y4U4 w0 = y4_ld_u4(nd), w1 = y4_ld_u4(nd + 1), w2 = y4_ld_u4(nd + 2), w3 = y4_ld_u4(nd + 3), w4 = y4_ld_u4(nd + 4);
+				const uint32_t hits = y4_node_hits<true>(w0, w1, w2, w3, w4, rc.o, rc.idir, rc.oct_inv, t_lo, t_hi, magic, pad);
+				ngroup.x = w1.x; ngroup.y = (hits & 0xff000000u) | (w0.w >> 24);
+				tgroup.x = w1.y; tgroup.y = hits & 0x00ffffffu;
+			}
+			else
+			{
+				tgroup = ngroup;
+				ngroup.y = 0u;
+			}
+			if(tgroup.y)
+			{
+				if(cur == Y4_INST_NONE)
+				{
+					// top level: enter the first instance of the group; the rest and the pending node group wait under the marker
+					const uint32_t bit = 31u - (uint32_t) __clz((int) tgroup.y);
+					tgroup.y &= ~(1u << bit);
+					const uint32_t id = y4_ld_tri(sc.tlas_leaves + tgroup.x + bit).prim;
+					if(ngroup.y & 0xff000000u) stack[sp++] = ngroup;
+					if(tgroup.y) stack[sp++] = tgroup;
+					uint2 mark; mark.x = 0xffffffffu; mark.y = 0u;
+					stack[sp++] = mark;
+					const Y4Inst in = y4_ld_inst(sc.inst + id);
+					cur = id; node_off = in.node_off;
+					V3 oo, od;
+					y4_inst_enter(in, wo, wd, oo, od, pad);
+					rc = y4_ray_ctx(oo, od);
+					ngroup.x = 0u; ngroup.y = (1u << (24u + rc.oct_inv)) | 1u;
+				}
+				else
+				{
+					const Y4Inst in = y4_ld_inst(sc.inst + cur);
+					while(tgroup.y)
+					{
+						const uint32_t bit = 31u - (uint32_t) __clz((int) tgroup.y);
+						tgroup.y &= ~(1u << bit);
+						const Y4TriObj tr = y4_ld_triobj(sc.blas_tris + in.tri_off + tgroup.x + bit);
+						float t, u, v;
+						if(!y4_inst_tri(in, tr, wo, wd, t, u, v)) continue;
+						if(!(tr.flags & vis_bit)) continue;
+						const uint32_t prim = in.first_prim + tr.prim_local;
+						if(!y4_accept_t<KIND>(t, t_lo, t_hi, prim, hit.prim)) continue;
+						hit.t = t; hit.bu = u; hit.bv = v; hit.prim = (int32_t) prim;
+						if(KIND == Y4_TRACE_CLOSEST) t_hi = t;
+						else { done = true; break; }
+					}
+				}
+			}
+			if(!done && (ngroup.y & 0xff000000u) == 0u)
+			{
+				while(true)
+				{
+					if(sp == 0) { done = true; break; }
+					ngroup = stack[--sp];
+					if(ngroup.x != 0xffffffffu || ngroup.y != 0u) break;
+					cur = Y4_INST_NONE; node_off = 0u; pad = 0.f; rc = y4_ray_ctx(wo, wd);      // the marker: back at the top level
+				}
+			}
+			if(done)
+			{
+				float4 o; o.x = hit.t; o.y = hit.bu; o.z = hit.bv; o.w = __int_as_float(hit.prim);
+				*reinterpret_cast<float4 *>(out + ray_i) = o;
+				have = false;
+				break;
+			}
+			if(__popc(__activemask()) < leave_below) break;
+		}
+		__syncwarp();
 	}
 }
 
@@ -302,7 +406,8 @@ int launch2(y4gpu_ctx *ctx, const TraceArgs &a)
 	const uint64_t want = (a.n + kTraceThreads - 1) / kTraceThreads;
 	const int use_per_sm = (a.max_blocks_per_sm > 0 && a.max_blocks_per_sm < per_sm) ? a.max_blocks_per_sm : per_sm;
 	const uint64_t full = (uint64_t) ctx->sm_count * use_per_sm;
-	k_trace2<KIND, QUEUE><<<(int) (want < full ? want : full), kTraceThreads, 0, a.stream>>>(ctx->view2(), a.rays, a.n, a.out, a.work_counter, a.queue, a.queue_count);
+	k_trace2<KIND, QUEUE><<<(int) (want < full ? want : full), kTraceThreads, 0, a.stream>>>(ctx->view2(), a.rays, a.n, a.out, a.work_counter,
+	                                                                                      a.fetch_threshold > 0 ? a.fetch_threshold : ctx->fetch_threshold, a.queue, a.queue_count);
 	return Y4GPU_OK;
 }
 template<int KIND, bool QUEUE>

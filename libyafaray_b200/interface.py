@@ -17,6 +17,8 @@ from __future__ import annotations
 import ctypes as C
 from typing import Dict, List, Optional
 
+import os
+
 import numpy as np
 
 from . import _lib, film_io, images
@@ -75,6 +77,10 @@ class Interface:
         self._cur_mat: Optional[str] = None
         self._next_id = 0
         self.accelerator: Optional[AcceleratorB200] = None
+        # instanced objects (addInstance): "auto" keeps the base meshes once on the device (two-level BVH8, results identical to the
+        # flattened scene) whenever the scene has instances and nothing needs the flat arrays (filtered transparent shadows do);
+        # False always flattens like the reference's scene does.  Env Y4GPU_INSTANCING=0/1 overrides.
+        self.device_instancing = "auto"
         self.film_buffers = None  # optional (weights, rgba) torch CUDA tensors installed by the caller
         self._pinned_film = None
         self.last_stats: dict = {}
@@ -391,12 +397,13 @@ class Interface:
             raise Y4Error(f"scene_accelerator '{acc}' is not provided by this back end (use '{ACCELERATOR_TYPE}')")
 
     # ---- scene assembly: what Scene::updateObjects + the factories hand to the back end --------------
-    def assemble(self):
+    def assemble(self, flatten: bool = True):
         """-> dict(tris [n,9] f32, flags [n] u32, normals [n,9] f32 | None, cam, mats, lights, params) in the
         reference's orders: objects by name (std::map, scene.cc:1034), faces in insertion order, lights by name."""
         mat_names = list(self.materials)
         mat_index = {n: i for i, n in enumerate(mat_names)}
         tris, flags, normals, any_normals = [], [], [], False
+        meshes, mesh_flags, mesh_index, inst_list, n_prims = [], [], {}, [], 0     # the two-level description of the same scene
         textured = any(m.get("_diffuse_chain") for m in self.materials.values())
         orcos, uvs = [], []
         base_cache: Dict[str, tuple] = {}      # per mesh: fp32 vertices, index array, flag words, normals (shared by its instances)
@@ -452,24 +459,34 @@ class Interface:
             if textured:      # NaN in the first float: no orco points / uv values on this mesh (see include/y4gpu.h)
                 orcos.append(oc if oc is not None else np.full((len(idx), 9), np.nan, np.float32))
                 uvs.append(uv if uv is not None else np.full((len(idx), 6), np.nan, np.float32))
-            if o.instance_of:  # Matrix4 * Point3 in fp32, matrix4.h:85-90
-                m = o.matrix
-                v = np.stack([((m[r, 0] * v[:, 0] + m[r, 1] * v[:, 1]) + m[r, 2] * v[:, 2]) + m[r, 3] for r in range(3)], -1).astype(np.float32)
-            tris.append(v[idx].reshape(-1, 9))
+            if base.name not in mesh_index:
+                mesh_index[base.name] = len(meshes)
+                meshes.append(np.ascontiguousarray(v[idx].reshape(-1, 9), np.float32))
+                mesh_flags.append(f)
+            inst_list.append((mesh_index[base.name], np.asarray(o.matrix, np.float32)[:3, :4].copy() if o.instance_of else None))
+            n_prims += len(idx)
+            if flatten:
+                if o.instance_of:  # Matrix4 * Point3 in fp32, matrix4.h:85-90
+                    m = o.matrix
+                    v = np.stack([((m[r, 0] * v[:, 0] + m[r, 1] * v[:, 1]) + m[r, 2] * v[:, 2]) + m[r, 3] for r in range(3)], -1).astype(np.float32)
+                tris.append(v[idx].reshape(-1, 9))
             if nn is not None and not o.instance_of:
                 normals.append(nn)
                 any_normals = True
             else:           # flat-shaded mesh in a scene that has smooth ones: NaN marks "shading normal = face normal" (include/y4gpu.h)
-                normals.append(np.full((len(idx), 9), np.nan, np.float32))
-            flags.append(f)
-        if tris:
+                normals.append(len(idx))          # (materialised below, and only when some mesh is smooth)
+            if flatten:
+                flags.append(f)
+        if not flatten:
+            T, F = None, None
+        elif tris:
             T = np.ascontiguousarray(np.concatenate(tris), np.float32)
             F = np.ascontiguousarray(np.concatenate(flags), np.uint32)
         else:
             T, F = np.zeros((0, 9), np.float32), np.zeros(0, np.uint32)
         N = None
         if any_normals:
-            N = np.ascontiguousarray(np.concatenate(normals), np.float32)
+            N = np.ascontiguousarray(np.concatenate([np.full((x, 9), np.nan, np.float32) if isinstance(x, int) else x for x in normals]), np.float32)
 
         rp = self.render_params
         integ = self.integrators[rp["integrator_name"]] if "integrator_name" in rp else next(iter(self.integrators.values()))
@@ -664,7 +681,9 @@ class Interface:
         pr.profile = int(rp.get("b200_profile", 0))
         tri_orco = np.ascontiguousarray(np.concatenate(orcos), np.float32) if layer_list and orcos else None
         tri_uv = np.ascontiguousarray(np.concatenate(uvs), np.float32) if layer_list and uvs else None
-        return {"_light_tris": self._light_tris,      # the object lights' vertex arrays the `lights` structs point into
+        return {"meshes": meshes, "mesh_flags": mesh_flags, "instances": inst_list, "n_prims": n_prims,
+                "any_instances": any(m is not None for _, m in inst_list),
+                "_light_tris": self._light_tris,      # the object lights' vertex arrays the `lights` structs point into
                 "tris": T, "flags": F, "normals": N, "cam": cam, "mats": mats, "n_mat": len(mat_names), "lights": lights,
                 "n_light": len(light_names), "params": pr, "textures": textures, "n_tex": len(tex_list), "layers": layers,
                 "n_layers": len(layer_list), "tri_orco": tri_orco, "tri_uv": tri_uv, "_texels": texel_arrays}
@@ -672,11 +691,17 @@ class Interface:
     # ---- render (Scene::render -> TiledIntegrator::render, integrator_tiled.cc:97-233) --------------
     def upload(self):
         """Geometry upload + BVH8 build + scene description (the accelerator/integrator preprocess step)."""
-        a = self.assemble()
-        if self.accelerator is not None and self.accelerator.ctx.value:
-            self.accelerator.rebuild(a["tris"], flags=a["flags"])       # same context: device allocations are reused
+        two_level = self._wants_two_level()
+        a = self.assemble(flatten=not two_level)
+        if two_level and not a["any_instances"]:
+            two_level, a = False, self.assemble()
+        if self.accelerator is None or not self.accelerator.ctx.value:
+            self.accelerator = AcceleratorB200(None, device=self.device)
+        if two_level:
+            self.accelerator.rebuild_instances(a["meshes"], a["instances"], a["mesh_flags"])
         else:
-            self.accelerator = AcceleratorB200(a["tris"], flags=a["flags"], device=self.device)
+            self.accelerator.rebuild(a["tris"], flags=a["flags"])       # same context: device allocations are reused
+        a["two_level"] = two_level
         L, ctx = self.accelerator._L, self.accelerator.ctx
         nptr = C.c_void_p(a["normals"].ctypes.data) if a["normals"] is not None else None
         optr = C.c_void_p(a["tri_orco"].ctypes.data) if a["tri_orco"] is not None else None
@@ -710,6 +735,20 @@ class Interface:
             _lib.check(ctx, L.y4gpu_pt_set_film_buffers(ctx, C.c_void_p(w.data_ptr()), C.c_void_p(rgba.data_ptr())), "y4gpu_pt_set_film_buffers")
         self._assembled = a
         return a
+
+    def _wants_two_level(self) -> bool:
+        mode = self.device_instancing
+        env = os.environ.get("Y4GPU_INSTANCING")
+        if env is not None:
+            mode = env not in ("0", "false", "")
+        if mode is False or not any(o.instance_of for o in self.objects.values()):
+            return False
+        if mode is True:
+            return True
+        # auto: filtered transparent shadows walk the flat tree only
+        integ = next(iter(self.integrators.values()), {}) if self.integrators else {}
+        transp = any(float(m.get("transparency", 0.0)) > 0.00001 for m in self.materials.values())
+        return not (bool(integ.get("transpShad", False)) and transp)
 
     @property
     def sharded(self) -> bool:

@@ -225,14 +225,23 @@ sys.path.insert(0, GOLD)
 from make_golden_large import CITY1M, CITY200K, RR_ON  # noqa: E402
 
 
+@pytest.mark.parametrize("instancing", [False, True])
 @pytest.mark.parametrize("key,cfg", [("city200k", CITY200K), ("city1m", CITY1M)])
-def test_c4_instanced_city_vs_reference_golden(key, cfg):
+def test_c4_instanced_city_vs_reference_golden(key, cfg, instancing):
     """BASELINE config C4 at sizes the reference renders in seconds: 200 k and 1 M instanced triangles (yafaray_addInstance),
-    8 bounces + NEE, against the committed reference PathIntegrator renders (tests/golden/make_golden_large.py)."""
+    8 bounces + NEE, against the committed reference PathIntegrator renders (tests/golden/make_golden_large.py) -- with the
+    instances flattened to world-space triangles, and kept as instances of shared meshes on the device (two-level BVH8)."""
     ref = np.load(os.path.join(GOLD, "pt_city_large.npz"))[key]
     yi = _gpu(**cfg)
+    yi.device_instancing = instancing
     img = yi.render()
-    assert yi._assembled["tris"].shape[0] >= 0.95 * cfg["n_tri_target"]
+    assert yi._assembled["n_prims"] >= 0.95 * cfg["n_tri_target"] and yi._assembled["two_level"] == instancing
+    if instancing:      # the same film as the flattened run: every ray finds the same hit
+        flat = _gpu(**cfg)
+        flat.device_instancing = False
+        assert np.abs(flat.render() - img).max() <= 2e-6 * max(1.0, float(ref.max()))        # (float atomics: the order of the film sums differs)
+        st_f, st_t = flat.accelerator.stats(), yi.accelerator.stats()
+        assert (st_t["node_bytes"] + st_t["tri_bytes"]) * 3 < st_f["node_bytes"] + st_f["tri_bytes"]
     assert helpers.psnr(img, ref) >= PSNR_MIN, helpers.psnr(img, ref)
     # sample-exact except where a path meets a near-tie between coplanar / touching building faces (instances overlap): those
     # pixel-samples take another but equally valid path -- well under 1 % of the pixels
