@@ -657,6 +657,7 @@ def pt_arm(args, env):
     torch.cuda.set_stream(stream)
     yi = make(comm=dist if world > 1 else None)
     yi.upload()
+    acc_stats = yi.accelerator.stats()
     yi.accelerator.set_stream(stream.cuda_stream)
 
     def step(k):
@@ -779,6 +780,10 @@ def pt_arm(args, env):
         "rays_per_sample": {"closest": st["rays_closest"] / st["samples"], "shadow": st["rays_shadow"] / st["samples"]},
         "mrays_s": (st["rays_closest"] + st["rays_shadow"]) / st["samples"] * value,
         "film_check": {"weight_sum": wsum, "mean_rgb": mean_rgb},
+        "accelerator": dict({k: acc_stats[k] for k in ("n_tris", "n_nodes", "node_bytes", "tri_bytes", "build_ms", "bvh_levels")},
+                            two_level=bool(yi._assembled.get("two_level")), instances=len(yi._assembled["instances"]), meshes=len(yi._assembled["meshes"]),
+                            note="node_bytes + tri_bytes = the resident accelerator (BVH8 nodes + leaf records [+ instance records]); a flat scene also "
+                                 "keeps 40 B per triangle of vertices and flag words, a two-level scene 40 B per BASE-mesh triangle"),
         "gpu_launches": int(launches),
         "roofline": {
             "bound": "hbm", "kernel": "%s kernels of one pass" % names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
