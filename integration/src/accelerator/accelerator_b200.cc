@@ -8,6 +8,7 @@
 #include "geometry/primitive/primitive_face.h"
 #include "geometry/primitive/primitive_instance.h"
 #include "geometry/object/object_instance.h"
+#include "geometry/object/object.h"
 #include "material/material.h"
 #include <cmath>
 #include <cstdlib>
@@ -112,7 +113,73 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 		}
 		mat_transparency[3 * mi] = colour[0].r_; mat_transparency[3 * mi + 1] = colour[0].g_; mat_transparency[3 * mi + 2] = colour[0].b_;
 	}
-	if(y4gpu_upload_triangles(ctx, verts.data(), flags.data(), n) != Y4GPU_OK || y4gpu_build(ctx, nullptr) != Y4GPU_OK)
+	// Instances stay instances on the device when the primitive list is what Scene::updateObjects produces for instanced objects:
+	// runs of PrimitiveInstance that walk their base object's faces in order under one obj_to_world matrix (primitive_instance.cc,
+	// object_instance.cc:25-33).  The meshes go up once in object space with one matrix per run (y4gpu_upload_instanced; results
+	// are identical to the flattened upload).  Anything else -- or Y4GPU_INSTANCING=0 -- uploads the world-space triangles.
+	bool two_level = false;
+	{
+		const char *e = getenv("Y4GPU_INSTANCING");
+		bool want = !(e && atoi(e) == 0), any_matrix = false;
+		for(size_t k = 0; k < n && want; ++k) want = !(flags[k] & Y4GPU_TRI_TRANSPARENT);      // intersectTs' filter colours walk the flat tree only
+		bool ok = want;
+		std::unordered_map<const Object *, uint32_t> mesh_of;
+		std::vector<std::vector<float>> mesh_verts;
+		std::vector<std::vector<uint32_t>> mesh_flags;
+		std::vector<y4gpu_instance> insts;
+		size_t i = 0;
+		while(ok && i < n)
+		{
+			const Matrix4 *m = nullptr;
+			const FacePrimitive *face = faceOf(primitives[i], &m);
+			const Object *obj = face->getObject();
+			const std::vector<const Primitive *> base = obj->getPrimitives();
+			const size_t bn = base.size();
+			if(bn == 0 || i + bn > n) { ok = false; break; }
+			for(size_t k = 0; k < bn && ok; ++k)
+			{
+				const Matrix4 *mk = nullptr;
+				ok = faceOf(primitives[i + k], &mk) == dynamic_cast<const FacePrimitive *>(base[k]) && mk == m;
+			}
+			if(!ok) break;
+			auto it = mesh_of.find(obj);
+			if(it == mesh_of.end())
+			{
+				it = mesh_of.emplace(obj, (uint32_t) mesh_verts.size()).first;
+				mesh_verts.emplace_back(9 * bn);
+				mesh_flags.emplace_back(flags.begin() + (long) i, flags.begin() + (long) (i + bn));
+				std::vector<float> &mv = mesh_verts.back();
+				for(size_t k = 0; k < bn; ++k)
+				{
+					const FacePrimitive *f = dynamic_cast<const FacePrimitive *>(base[k]);
+					for(int c = 0; c < 3; ++c) { const Point3 p = f->getVertex(c); mv[9 * k + 3 * c] = p.x(); mv[9 * k + 3 * c + 1] = p.y(); mv[9 * k + 3 * c + 2] = p.z(); }
+				}
+			}
+			else
+			{
+				const std::vector<uint32_t> &mf = mesh_flags[it->second];      // the flag words are per mesh triangle: every run must agree
+				for(size_t k = 0; k < bn && ok; ++k) ok = mf[k] == flags[i + k];
+				if(!ok) break;
+			}
+			y4gpu_instance in;
+			in.mesh = it->second; in.identity = m ? 0u : 1u;
+			const float id[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+			for(int r = 0; r < 3; ++r) for(int c = 0; c < 4; ++c) in.obj_to_world[4 * r + c] = m ? (*m)[r][c] : id[4 * r + c];
+			insts.push_back(in);
+			any_matrix = any_matrix || m;
+			i += bn;
+		}
+		if(ok && any_matrix)
+		{
+			std::vector<y4gpu_mesh> ms(mesh_verts.size());
+			for(size_t k = 0; k < ms.size(); ++k) { ms[k].v_xyz = mesh_verts[k].data(); ms[k].flags = mesh_flags[k].data(); ms[k].n_tri = mesh_flags[k].size(); }
+			two_level = y4gpu_upload_instanced(ctx, ms.data(), (uint32_t) ms.size(), insts.data(), (uint32_t) insts.size()) == Y4GPU_OK
+			            && y4gpu_build(ctx, nullptr) == Y4GPU_OK;
+			if(!two_level) logger.logWarning("AcceleratorB200: two-level upload failed (", y4gpu_last_error(ctx), "), uploading world-space triangles");
+			else logger.logInfo("AcceleratorB200: ", insts.size(), " instances of ", ms.size(), " meshes kept as instances on the device");
+		}
+	}
+	if(!two_level && (y4gpu_upload_triangles(ctx, verts.data(), flags.data(), n) != Y4GPU_OK || y4gpu_build(ctx, nullptr) != Y4GPU_OK))
 	{
 		logger.logError("AcceleratorB200: ", y4gpu_last_error(ctx));
 		y4gpu_destroy(ctx);
