@@ -160,6 +160,16 @@ int y4gpu_upload_instanced(y4gpu_ctx *ctx, const y4gpu_mesh *meshes, uint32_t n_
 	{
 		if(instances[i].mesh >= n_mesh) { ctx->err = "instance refers to a mesh that was not given"; return Y4GPU_ERR_ARG; }
 		total += meshes[instances[i].mesh].n_tri;
+		if(!instances[i].identity)
+		{
+			// the walk maps rays into object space: the matrix must be invertible (a collapsed instance can still be uploaded flattened)
+			const float *m = instances[i].obj_to_world;
+			const double det = (double) m[0] * ((double) m[5] * m[10] - (double) m[6] * m[9]) - (double) m[1] * ((double) m[4] * m[10] - (double) m[6] * m[8])
+			                   + (double) m[2] * ((double) m[4] * m[9] - (double) m[5] * m[8]);
+			double mag = 0.0;
+			for(int k = 0; k < 12; ++k) { if(!(m[k] == m[k]) || fabs((double) m[k]) > 1e30) mag = -1.0; else if((k & 3) != 3 && mag >= 0.0) mag = fmax(mag, fabs((double) m[k])); }
+			if(mag < 0.0 || !(fabs(det) > 1e-12 * mag * mag * mag)) { ctx->err = "singular or non-finite instance matrix (upload such a scene as flattened triangles)"; return Y4GPU_ERR_UNSUPPORTED; }
+		}
 	}
 	if(total > 0x3fffffffull || first[n_mesh] > 0x3fffffffull) { ctx->err = "too many triangles (max 2^30-1)"; return Y4GPU_ERR_ARG; }
 	ctx->two_level = true;
@@ -185,11 +195,13 @@ int y4gpu_upload_instanced(y4gpu_ctx *ctx, const y4gpu_mesh *meshes, uint32_t n_
 		Y4_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	}
 	ctx->mesh_first = first;
-	ctx->h_inst.resize(n_inst);
 	uint32_t first_prim = 0;
+	ctx->h_inst.clear();
 	for(uint32_t i = 0; i < n_inst; ++i)
 	{
-		Y4Inst &in = ctx->h_inst[i];
+		if(meshes[instances[i].mesh].n_tri == 0) continue;          // an instance of an empty mesh owns no primitives
+		ctx->h_inst.emplace_back();
+		Y4Inst &in = ctx->h_inst.back();
 		memset(&in, 0, sizeof(in));
 		memcpy(in.m, instances[i].obj_to_world, sizeof(in.m));
 		in.mesh = instances[i].mesh; in.identity = instances[i].identity ? 1u : 0u;

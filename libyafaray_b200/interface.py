@@ -698,8 +698,12 @@ class Interface:
         if self.accelerator is None or not self.accelerator.ctx.value:
             self.accelerator = AcceleratorB200(None, device=self.device)
         if two_level:
-            self.accelerator.rebuild_instances(a["meshes"], a["instances"], a["mesh_flags"])
-        else:
+            try:
+                self.accelerator.rebuild_instances(a["meshes"], a["instances"], a["mesh_flags"])
+            except Y4Error as e:      # e.g. a singular instance matrix: the flattened scene is always possible
+                self.warnings.append(f"two-level upload refused ({e}); uploading flattened triangles")
+                two_level, a = False, self.assemble()
+        if not two_level:
             self.accelerator.rebuild(a["tris"], flags=a["flags"])       # same context: device allocations are reused
         a["two_level"] = two_level
         L, ctx = self.accelerator._L, self.accelerator.ctx

@@ -210,6 +210,12 @@ def test_two_level_instanced_scene_equals_the_flattened_upload():
         assert np.array_equal(d_out.cpu().numpy().view(np.uint32).reshape(-1), h1.view(np.uint32).reshape(-1))
     with pytest.raises(Exception):
         a_two.isShadowedTransparent(rays[:16], 4, np.ones((1, 3), np.float32))      # filtered shadows: flat scenes only
+    # a collapsed instance cannot be walked in object space: refused (the Interface then uploads the flattened scene); an instance
+    # of an empty mesh owns no primitives and changes nothing
+    with pytest.raises(Exception, match="singular"):
+        AcceleratorB200.from_instances(meshes, inst + [(0, [1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 0])])
+    a_e = AcceleratorB200.from_instances(meshes + [np.zeros((0, 9), np.float32)], inst + [(len(meshes), None)], leaf_max=3)
+    assert np.array_equal(a_e.intersect(rays).view(np.uint32), h1.view(np.uint32))
     # back to a flat scene in the same context
     a_two.rebuild(flat[:1000])
     assert np.array_equal(a_two.intersect(rays[:1000]).view(np.uint32), AcceleratorB200(flat[:1000]).intersect(rays[:1000]).view(np.uint32))

@@ -12,6 +12,8 @@ CLASSES = [  # (regex on the demangled kernel name, class name as bench.py print
     (r"k_pt_gen\(", "camera rays"),
     (r"k_trace<0", "trace_closest"),
     (r"k_trace<1", "trace_shadow"),
+    (r"k_trace2<0", "trace_closest"),
+    (r"k_trace2<1", "trace_shadow"),
     (r"k_trace_tshadow", "trace_shadow"),
     (r"k_pt_stage<1", "extra light-sample stages"),
     (r"k_pt_path_compact<", "path stages (camera hit, start, per-bounce)"),
