@@ -358,8 +358,8 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 			else if(type == "sunlight") { l.type = Y4GPU_LIGHT_SUN; l.samples = get<int>(p, "samples", 4); l.angle = get<float>(p, "angle", 0.27f); put3(l.point1, getVec(p, "direction", Vec3{0.f, 0.f, 1.f})); }
 			else if(type == "spotlight")
 			{
-				if(get<bool>(p, "soft_shadows", false)) unsupported("spotlight soft_shadows");
 				l.type = Y4GPU_LIGHT_SPOT; l.angle = get<float>(p, "cone_angle", 45.f); l.blend = get<float>(p, "blend", 0.15f);
+				if(get<bool>(p, "soft_shadows", false)) { l.type = Y4GPU_LIGHT_SPOT_SOFT; l.samples = get<int>(p, "samples", 8); l.radius = get<float>(p, "shadowFuzzyness", 1.f); }
 				put3(l.from, getVec(p, "from", Vec3{0.f})); put3(l.point1, getVec(p, "to", Vec3{0.f, 0.f, -1.f}));
 			}
 			else if(type == "spherelight") { l.type = Y4GPU_LIGHT_SPHERE; l.samples = get<int>(p, "samples", 4); l.radius = get<float>(p, "radius", 1.f); put3(l.from, getVec(p, "from", Vec3{0.f})); }

@@ -212,9 +212,14 @@ inline Y4PtLight derive_light(const y4gpu_pt_light &l)
 		o.color = c3(o.color.r * o.pdf, o.color.g * o.pdf, o.color.b * o.pdf);            // col_pdf_
 		return o;
 	}
-	if(l.type == Y4GPU_LIGHT_SPOT)                        // SpotLight ctor (light_spot.cc:30-43), soft_shadows_ == false
+	if(l.type == Y4GPU_LIGHT_SPOT || l.type == Y4GPU_LIGHT_SPOT_SOFT)      // SpotLight ctor (light_spot.cc:30-43)
 	{
 		o.dir = tov(normalized(hv(l.from) - hv(l.point1)));                                // ndir_ = (from - to).normalize()
+		if(l.type == Y4GPU_LIGHT_SPOT_SOFT)
+		{
+			y4_coords_system(xneg(o.dir), o.du, o.dv);                                     // createCoordsSystem(dir_), dir_ = -ndir_
+			o.radius = l.radius;                                                           // shadow_fuzzy_
+		}
 		const double rad_angle = (double) (float) ((long double) l.angle * 0.01745329251994329576923690768489L);
 		const double rad_inner_angle = rad_angle * (double) (1.f - l.blend);
 		o.cos_start = y4_fast_cos((float) rad_inner_angle);

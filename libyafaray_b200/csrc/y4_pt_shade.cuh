@@ -566,6 +566,28 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 		ls.tmax = -1.f;
 		return true;
 	}
+	if(GENERAL && L.type == Y4GPU_LIGHT_SPOT_SOFT)        // SpotLight::illumSample (light_spot.cc:106-144)
+	{
+		V3 ldir = xsub3(L.pos, from);
+		const float dist_sqr = xdot(ldir, ldir);
+		if(dist_sqr == 0.f) return false;
+		const float dist = xsqrt(dist_sqr);
+		ldir = xscale(ldir, xdiv(1.f, dist));
+		const float cosa = xdot(L.dir, ldir);
+		if(cosa < L.cos_end) return false;
+		ls.tmax = dist;
+		ls.dir = y4_sample_cone(ldir, L.du, L.dv, L.cos_end, xmul(s1, L.radius), xmul(s2, L.radius));
+		if(cosa >= L.cos_start) ls.col = L.color;
+		else
+		{
+			float v = xmul(xsub(cosa, L.cos_end), L.icos_diff);
+			v = xmul(xmul(v, v), xsub(3.f, xmul(2.f, v)));
+			ls.col = cscale(L.color, v);
+		}
+		ls.pdf = dist_sqr;
+		if(ls.pdf < 1.f) { ls.pdf = 1.f; ls.col = cdiv(ls.col, dist_sqr); }
+		return true;
+	}
 	if(L.type == Y4GPU_LIGHT_SUN)
 	{
 		ls.dir = y4_sample_cone(L.dir, L.du, L.dv, L.cos_angle, s1, s2);
@@ -628,6 +650,33 @@ Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, f
 		col = y4_bg_eval(L, y4_inv_sphere_map(u, v));
 		t = -1.f;
 		return true;
+	}
+	if(GENERAL && L.type == Y4GPU_LIGHT_SPOT_SOFT)        // SpotLight::intersect (light_spot.cc:199-246); dir_ = -ndir_
+	{
+		const V3 sdir = xneg(L.dir);
+		const float cos_a = xdot(sdir, dir);
+		if(cos_a == 0.f) return false;
+		t = xdiv(xdot(sdir, xsub3(L.pos, from)), cos_a);
+		if(t < 0.f) return false;
+		const V3 p = xadd3(from, xscale(dir, t));
+		if(xdot(sdir, xsub3(p, L.pos)) == 0.f)
+		{
+			if(xdot(p, p) <= 1e-2f)
+			{
+				const float cosa = xdot(sdir, dir);
+				if(cosa < L.cos_end) return false;
+				if(cosa >= L.cos_start) col = L.color;
+				else
+				{
+					float v = xmul(xsub(cosa, L.cos_end), L.icos_diff);
+					v = xmul(xmul(v, v), xsub(3.f, xmul(2.f, v)));
+					col = cscale(L.color, v);
+				}
+				ipdf = xdiv(1.f, xmul(t, t));
+				return true;
+			}
+		}
+		return false;
 	}
 	if(L.type == Y4GPU_LIGHT_SUN)
 	{

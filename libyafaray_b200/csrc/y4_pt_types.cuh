@@ -109,7 +109,7 @@ struct Y4PtLight
 };
 // Light::diracLight() / Light::canIntersect() of the supported lights (include/light/light_*.h)
 Y4_HD bool y4_light_dirac(int type) { return type == Y4GPU_LIGHT_POINT || type == Y4GPU_LIGHT_DIRECTIONAL || type == Y4GPU_LIGHT_SPOT; }
-Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN || type == Y4GPU_LIGHT_OBJECT || type == Y4GPU_LIGHT_BACKGROUND; }
+Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN || type == Y4GPU_LIGHT_OBJECT || type == Y4GPU_LIGHT_BACKGROUND || type == Y4GPU_LIGHT_SPOT_SOFT; }
 
 #define Y4_PT_MAX_LIGHTS 64
 #define Y4_FILTER_TABLE 16

@@ -258,8 +258,6 @@ class Interface:
         p = dict(self.params)
         if p.get("type") not in ("pointlight", "arealight", "directional", "sunlight", "spherelight", "spotlight", "objectlight", "meshlight"):
             raise Y4Error(f"light type '{p.get('type')}' is not supported by the GPU back end")
-        if p.get("type") == "spotlight" and p.get("soft_shadows", False):
-            raise Y4Error("spotlight soft_shadows is not supported by the GPU back end")
         self.lights[name] = p
         return True
 
@@ -613,6 +611,8 @@ class Interface:
                 l.point1[:] = p.get("direction", (0.0, 0.0, 1.0))
             elif p["type"] == "spotlight":         # SpotLight::factory (light_spot.cc:250-288), soft_shadows = false
                 l.type, l.angle, l.blend = _lib.LIGHT_SPOT, float(p.get("cone_angle", 45.0)), float(p.get("blend", 0.15))
+                if p.get("soft_shadows", False):       # a sampled light: SpotLight::illumSample / intersect
+                    l.type, l.samples, l.radius = _lib.LIGHT_SPOT_SOFT, int(p.get("samples", 8)), float(p.get("shadowFuzzyness", 1.0))
                 l.from_[:] = p.get("from", (0.0, 0.0, 0.0))
                 l.point1[:] = p.get("to", (0.0, 0.0, -1.0))
             elif p["type"] in ("objectlight", "meshlight"):     # ObjectLight::factory (light_object_light.cc:222-253)

@@ -202,7 +202,7 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
             api.paramsSetFloat("radius", 0.22)
             api.paramsSetColor("color", 1.0, 0.4, 0.3, 1.0)
             api.paramsSetFloat("power", 1.5)
-        elif kind == "spot":                            # from the front opening onto the short box, wide blend
+        elif kind in ("spot", "spot_soft"):             # from the front opening onto the short box, wide blend
             api.paramsSetString("type", "spotlight")
             api.paramsSetVector("from", 0.75, 0.6, -0.9)
             api.paramsSetVector("to", 0.35, 0.2, 0.4)
@@ -210,6 +210,10 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
             api.paramsSetFloat("blend", 0.5)
             api.paramsSetColor("color", 0.9, 0.6, 1.0, 1.0)
             api.paramsSetFloat("power", 2.5)
+            if kind == "spot_soft":                     # a sampled light: cone-jittered shadow rays
+                api.paramsSetBool("soft_shadows", True)
+                api.paramsSetFloat("shadowFuzzyness", 0.7)
+                api.paramsSetInt("samples", light_samples)
         elif kind == "sphere":
             api.paramsSetString("type", "spherelight")
             api.paramsSetVector("from", 0.2, 0.75, 0.3)

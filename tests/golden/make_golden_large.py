@@ -12,6 +12,7 @@ UNMODIFIED reference (oracle/_ref), committed so that the GPU box can check them
   pt_glass.npz      <- Cornell box with `glass` objects (PT_GOLDEN_GLASS): reference PathIntegrator / DirectLightIntegrator, deterministic mode
   pt_ibl.npz        <- Cornell box lit by an IBL background light (PT_GOLDEN_IBL), deterministic mode
   pt_shiny2.npz     <- Cornell box with a shinydiffusemat sheet that is mirror AND transparent (PT_GOLDEN_SHINY2), deterministic mode
+  pt_spot_soft.npz  <- Cornell box lit by a spotlight with soft_shadows = true (PT_GOLDEN_SPOT_SOFT), deterministic mode
   pt_rr.npz         <- Cornell box with the integrator's default Russian roulette (russian_roulette_min_bounces = 0), 1024 spp
 
 Run from the repo root:  python tests/golden/make_golden_large.py [soup|city]
@@ -141,6 +142,24 @@ def make_shiny2():
     np.savez_compressed(os.path.join(HERE, "pt_shiny2.npz"), **out)
 
 
+# spotlight with soft_shadows = true (SpotLight::illumSample / intersect) -> pt_spot_soft.npz
+PT_GOLDEN_SPOT_SOFT = {
+    "spot_soft_direct": dict(width=96, height=54, spp=3, bounces=3, integrator="directlighting", lamp=False, extra_lights=("spot_soft",), light_samples=3),
+    "spot_soft_path_only_light": dict(width=80, height=45, spp=3, bounces=4, lamp=False, extra_lights=("spot_soft",), light_samples=1),
+    "spot_soft_direct_with_lamp": dict(width=80, height=45, spp=2, bounces=3, integrator="directlighting", extra_lights=("spot_soft",), light_samples=2, filter_type="gauss"),
+}
+
+
+def make_spot_soft():
+    out = {}
+    for key, kw in PT_GOLDEN_SPOT_SOFT.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print(key, float(out[key][..., :3].mean()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_spot_soft.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -167,6 +186,8 @@ if __name__ == "__main__":
         make_ibl()
     if "shiny2" in what:
         make_shiny2()
+    if "spot_soft" in what:
+        make_spot_soft()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

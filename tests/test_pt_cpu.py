@@ -178,8 +178,7 @@ def test_interface_rejects_unsupported_features():
     with pytest.raises(Y4Error):
         yi.createLight("l")
     yi.paramsClearAll()
-    yi.paramsSetString("type", "spotlight")
-    yi.paramsSetBool("soft_shadows", True)
+    yi.paramsSetString("type", "ieslight")
     with pytest.raises(Y4Error):
         yi.createLight("l")
     yi.paramsClearAll()
@@ -420,6 +419,26 @@ def test_object_light_vs_live_reference(variant):
     a = _assemble(**kw)
     w, rgba = helpers.emu_pt_render(a, ref_light_order=a["n_light"] > 1 and a["params"].path_samples > 0)
     assert helpers.psnr(interface.normalize_film(w, rgba), ref) >= 100.0
+
+
+def _spot_soft_cfgs():
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_SPOT_SOFT
+    return PT_GOLDEN_SPOT_SOFT
+
+
+@pytest.mark.parametrize("key", ["spot_soft_direct", "spot_soft_path_only_light", "spot_soft_direct_with_lamp"])
+def test_soft_spot_light_vs_golden_reference_render(key):
+    """spotlight with soft_shadows = true: a sampled light (cone-jittered shadow rays around the direction to the light,
+    pdf = squared distance with the reference's `pdf >= 1` patch; SpotLight::illumSample / intersect)."""
+    ref = np.load(os.path.join(GOLD, "pt_spot_soft.npz"))[key]
+    a = _assemble(**_spot_soft_cfgs()[key])
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
 def _shiny2_cfgs():
