@@ -234,11 +234,14 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow_queue(Y4Bvh8 bv
 // Two-level scenes: the walk of y4_trace_ray2 (y4_trace.cuh) with k_trace's warp scheduling -- lanes whose ray ended are
 // refilled from the work counter as soon as fewer than fetch_threshold lanes are busy.  Per-lane state between steps: the
 // world ray, the current space's ray (world or the instance's object space), the instance index and its tree offsets.
-template<int KIND, bool QUEUE>
+// COUNT: visit counters as in k_trace (visit[0] nodes of either level, visit[1] triangle tests, visit[2] live rays); an instance
+// entry -- its 48-byte top-level leaf record + the 128-byte instance record -- is counted as two nodes (160 B).
+template<int KIND, bool QUEUE, bool COUNT>
 __global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const Y4Ray *__restrict__ rays, uint64_t n, Y4Hit *__restrict__ out,
-                                                             unsigned long long *__restrict__ work_counter, int fetch_threshold,
+                                                             unsigned long long *__restrict__ work_counter, unsigned long long *__restrict__ visit, int fetch_threshold,
                                                              const uint32_t *__restrict__ queue, const uint32_t *__restrict__ queue_count)
 {
+	unsigned long long my_nodes = 0, my_tris = 0, my_live = 0;
 	if(QUEUE) n = __ldg(queue_count);
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t lt_mask = (1u << lane) - 1u;
@@ -278,6 +281,7 @@ __global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const 
 				hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
 				ray_i = slot_i; sp = 0; have = true; cur = Y4_INST_NONE; node_off = 0u;
 				ngroup.x = 0u; ngroup.y = (sc.n_inst && pr.t_hi > pr.t_lo) ? ((1u << (24u + rc.oct_inv)) | 1u) : 0u;
+				if(COUNT && ngroup.y) my_live++;
 			}
 		}
 		if(!__any_sync(0xffffffffu, have)) break;
@@ -295,6 +299,7 @@ __global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const 
 				if(ngroup.y & 0xff000000u) stack[sp++] = ngroup;
 				const Y4U4 *nd = (cur == Y4_INST_NONE ? sc.tlas_nodes : sc.blas_nodes + (size_t) node_off * Y4_NODE_WORDS) + (size_t) child * Y4_NODE_WORDS;
 				const Y4U4 w0 = y4_ld_u4(nd), w1 = y4_ld_u4(nd + 1), w2 = y4_ld_u4(nd + 2), w3 = y4_ld_u4(nd + 3), w4 = y4_ld_u4(nd + 4);
+				if(COUNT) my_nodes++;
 				const uint32_t hits = y4_node_hits<true>(w0, w1, w2, w3, w4, rc.o, rc.idir, rc.oct_inv, t_lo, t_hi, magic, pad);
 				ngroup.x = w1.x; ngroup.y = (hits & 0xff000000u) | (w0.w >> 24);
 				tgroup.x = w1.y; tgroup.y = hits & 0x00ffffffu;
@@ -317,6 +322,7 @@ __global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const 
 					uint2 mark; mark.x = 0xffffffffu; mark.y = 0u;
 					stack[sp++] = mark;
 					const Y4Inst in = y4_ld_inst(sc.inst + id);
+					if(COUNT) my_nodes += 2;
 					cur = id; node_off = in.node_off;
 					V3 oo, od;
 					y4_inst_enter(in, wo, wd, oo, od, pad);
@@ -331,6 +337,7 @@ __global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const 
 						const uint32_t bit = 31u - (uint32_t) __clz((int) tgroup.y);
 						tgroup.y &= ~(1u << bit);
 						const Y4TriObj tr = y4_ld_triobj(sc.blas_tris + in.tri_off + tgroup.x + bit);
+						if(COUNT) my_tris++;
 						float t, u, v;
 						if(!y4_inst_tri(in, tr, wo, wd, t, u, v)) continue;
 						if(!(tr.flags & vis_bit)) continue;
@@ -363,6 +370,17 @@ __global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const 
 		}
 		__syncwarp();
 	}
+	if(COUNT)
+	{
+#pragma unroll
+		for(int o = 16; o > 0; o >>= 1)
+		{
+			my_nodes += __shfl_xor_sync(0xffffffffu, my_nodes, o);
+			my_tris += __shfl_xor_sync(0xffffffffu, my_tris, o);
+			my_live += __shfl_xor_sync(0xffffffffu, my_live, o);
+		}
+		if(lane == 0) { atomicAdd(visit, my_nodes); atomicAdd(visit + 1, my_tris); atomicAdd(visit + 2, my_live); }
+	}
 }
 
 struct TraceArgs
@@ -393,27 +411,27 @@ int launch_k(y4gpu_ctx *ctx, const TraceArgs &a)
 	                                                                          a.fetch_threshold > 0 ? a.fetch_threshold : ctx->fetch_threshold, ctx->postpone_div, a.queue, a.queue_count);
 	return Y4GPU_OK;
 }
-template<int KIND, bool QUEUE>
+template<int KIND, bool QUEUE, bool COUNT>
 int launch2(y4gpu_ctx *ctx, const TraceArgs &a)
 {
 	static int per_sm_cached[16] = {0};
 	int &per_sm = per_sm_cached[ctx->device & 15];
 	if(per_sm < 1)
 	{
-		Y4_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace2<KIND, QUEUE>, kTraceThreads, 0));
+		Y4_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace2<KIND, QUEUE, COUNT>, kTraceThreads, 0));
 		if(per_sm < 1) per_sm = 1;
 	}
 	const uint64_t want = (a.n + kTraceThreads - 1) / kTraceThreads;
 	const int use_per_sm = (a.max_blocks_per_sm > 0 && a.max_blocks_per_sm < per_sm) ? a.max_blocks_per_sm : per_sm;
 	const uint64_t full = (uint64_t) ctx->sm_count * use_per_sm;
-	k_trace2<KIND, QUEUE><<<(int) (want < full ? want : full), kTraceThreads, 0, a.stream>>>(ctx->view2(), a.rays, a.n, a.out, a.work_counter,
-	                                                                                      a.fetch_threshold > 0 ? a.fetch_threshold : ctx->fetch_threshold, a.queue, a.queue_count);
+	k_trace2<KIND, QUEUE, COUNT><<<(int) (want < full ? want : full), kTraceThreads, 0, a.stream>>>(ctx->view2(), a.rays, a.n, a.out, a.work_counter, a.visit,
+	                                                                                             a.fetch_threshold > 0 ? a.fetch_threshold : ctx->fetch_threshold, a.queue, a.queue_count);
 	return Y4GPU_OK;
 }
 template<int KIND, bool QUEUE>
 int launch(y4gpu_ctx *ctx, bool counted, const TraceArgs &a)
 {
-	if(ctx->two_level) return launch2<KIND, QUEUE>(ctx, a);        // (no visit counters in the two-level kernel)
+	if(ctx->two_level) return counted ? launch2<KIND, QUEUE, true>(ctx, a) : launch2<KIND, QUEUE, false>(ctx, a);
 	if(counted) return launch_k<KIND, true, 3, QUEUE>(ctx, a);
 	return ctx->min_blocks >= 4 ? launch_k<KIND, false, 4, QUEUE>(ctx, a) : launch_k<KIND, false, 3, QUEUE>(ctx, a);
 }

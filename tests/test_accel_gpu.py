@@ -208,6 +208,9 @@ def test_two_level_instanced_scene_equals_the_flattened_upload():
         a_two.intersect(d_rays, d_out)
         a_two.synchronize()
         assert np.array_equal(d_out.cpu().numpy().view(np.uint32).reshape(-1), h1.view(np.uint32).reshape(-1))
+    a_two.intersect(rays, counted=True)
+    st = a_two.stats()
+    assert st["nodes_visited"] > len(rays) and st["tris_tested"] > 0           # visit counters (the roofline's algorithmic bytes)
     with pytest.raises(Exception):
         a_two.isShadowedTransparent(rays[:16], 4, np.ones((1, 3), np.float32))      # filtered shadows: flat scenes only
     # a collapsed instance cannot be walked in object space: refused (the Interface then uploads the flattened scene); an instance
