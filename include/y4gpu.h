@@ -111,7 +111,7 @@ int y4gpu_upload_triangles(y4gpu_ctx *ctx, const float *v_xyz, const uint32_t *f
  * the indices of the flattened scene; results are bit-identical to uploading the flattened triangles: the device keeps the
  * meshes once (a top-level BVH8 over instances, one bottom-level BVH8 per mesh) and transforms a triangle's vertices to world
  * space per test like the reference does.  flags may be NULL per mesh (all visible, opaque, material 0).
- * Not available on such a scene: y4gpu_trace_tshadow* (filter colours).  y4gpu_trace_counted counts an instance entry as two nodes. */
+ * Every query works on such a scene; y4gpu_trace_counted counts an instance entry as two nodes. */
 typedef struct y4gpu_mesh { const float *v_xyz; const uint32_t *flags; uint64_t n_tri; } y4gpu_mesh;
 typedef struct y4gpu_instance { uint32_t mesh; uint32_t identity; float obj_to_world[12]; } y4gpu_instance;
 int y4gpu_upload_instanced(y4gpu_ctx *ctx, const y4gpu_mesh *meshes, uint32_t n_mesh, const y4gpu_instance *instances, uint32_t n_inst);

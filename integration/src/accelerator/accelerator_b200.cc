@@ -121,7 +121,6 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 	{
 		const char *e = getenv("Y4GPU_INSTANCING");
 		bool want = !(e && atoi(e) == 0), any_matrix = false;
-		for(size_t k = 0; k < n && want; ++k) want = !(flags[k] & Y4GPU_TRI_TRANSPARENT);      // intersectTs' filter colours walk the flat tree only
 		bool ok = want;
 		std::unordered_map<const Object *, uint32_t> mesh_of;
 		std::vector<std::vector<float>> mesh_verts;

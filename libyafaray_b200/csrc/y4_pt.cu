@@ -699,7 +699,6 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 			mat_transp[3 * i] = accum * tc.r; mat_transp[3 * i + 1] = accum * tc.g; mat_transp[3 * i + 2] = accum * tc.b;
 			if(params->transp_shadows) sc.tshadow_filter = 1;
 		}
-	if(sc.tshadow_filter && ctx->two_level) { ctx->err = "filtered transparent shadows (transpShad with transparent materials) need the flattened scene: upload the triangles instead of instances"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(sc.tshadow_filter)
 	{
 		if(n_mat > pt->mat_transp_cap) { cudaFree(pt->d_mat_transp); pt->d_mat_transp = nullptr; pt->mat_transp_cap = 0; }

@@ -151,7 +151,8 @@ __global__ void __launch_bounds__(kTraceThreads, MINB) k_trace(Y4Bvh8 bvh, const
 // Transparent shadows (reference intersectTs, accelerator_kdtree.cc:911-1061): distinct
 // transparent primitives multiply their material's transparency colour; an opaque blocker or
 // more than max_depth transparent layers means shadowed.
-__global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, const Y4Ray *__restrict__ rays, uint64_t n, int max_depth,
+template<bool TWO>
+__global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, Y4Scene2 sc2, const Y4Ray *__restrict__ rays, uint64_t n, int max_depth,
                                                                  const float *__restrict__ mat_transp, uint32_t n_mat, y4gpu_tshit *__restrict__ out,
                                                                  uint32_t *__restrict__ work_counter, int inner)
 {
@@ -179,7 +180,8 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, con
 			pr.o = v3(r.ox, r.oy, r.oz); pr.t_lo = r.tmin; pr.t_hi = (r.tmax >= 0.f) ? r.tmax : INFINITY;
 		}
 		Y4Hit h; int n_filt = 0;
-		y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, h, stack, nullptr, filt, filt_mat, &n_filt, max_depth);
+		if(TWO) y4_trace_ray2<Y4_TRACE_TSHADOW>(sc2, pr, h, stack, nullptr, filt, filt_mat, &n_filt, max_depth);
+		else y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, h, stack, nullptr, filt, filt_mat, &n_filt, max_depth);
 		float fr = 1.f, fg = 1.f, fb = 1.f;
 		for(int k = 0; k < n_filt; ++k)
 		{
@@ -195,7 +197,8 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow(Y4Bvh8 bvh, con
 
 // The same over an index queue of the path tracer: the filter colour goes into the hit record's t / bu / bv lanes
 // (prim >= 0: shadowed).  One packet counter per launch (a zeroed 64-bit slot of the pass).
-__global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow_queue(Y4Bvh8 bvh, const Y4Ray *__restrict__ rays, const uint32_t *__restrict__ queue,
+template<bool TWO>
+__global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow_queue(Y4Bvh8 bvh, Y4Scene2 sc2, const Y4Ray *__restrict__ rays, const uint32_t *__restrict__ queue,
                                                                        const uint32_t *__restrict__ queue_count, int max_depth, const float *__restrict__ mat_transp,
                                                                        uint32_t n_mat, Y4Hit *__restrict__ out, unsigned long long *__restrict__ work_counter)
 {
@@ -220,7 +223,11 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow_queue(Y4Bvh8 bv
 		const Y4PreparedRay pr = y4_prepare_ray(r, Y4_TRACE_TSHADOW);
 		Y4Hit h; h.t = 0.f; h.bu = 0.f; h.bv = 0.f; h.prim = -1;
 		int n_filt = 0;
-		if(pr.t_hi > pr.t_lo) y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, h, stack, nullptr, filt, filt_mat, &n_filt, max_depth);
+		if(pr.t_hi > pr.t_lo)
+		{
+			if(TWO) y4_trace_ray2<Y4_TRACE_TSHADOW>(sc2, pr, h, stack, nullptr, filt, filt_mat, &n_filt, max_depth);
+			else y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, h, stack, nullptr, filt, filt_mat, &n_filt, max_depth);
+		}
 		float fr = 1.f, fg = 1.f, fb = 1.f;
 		for(int k = 0; k < n_filt; ++k)
 		{
@@ -622,9 +629,9 @@ int y4_launch_trace_wave(y4gpu_ctx *ctx, int kind, bool counted, const Y4Ray *d_
 int y4_launch_tshadow_wave(y4gpu_ctx *ctx, const Y4Ray *d_rays, Y4Hit *d_out, const uint32_t *d_queue, const uint32_t *d_queue_count, int max_depth,
                            const float *d_mat_transp, uint32_t n_mat, unsigned long long *d_work_counter, cudaStream_t stream, int max_blocks_per_sm)
 {
-	if(ctx->two_level) { ctx->err = "filtered transparent shadows are not available on a two-level (instanced) scene"; return Y4GPU_ERR_UNSUPPORTED; }
 	const int per_sm = max_blocks_per_sm > 0 && max_blocks_per_sm < 4 ? max_blocks_per_sm : 4;
-	k_trace_tshadow_queue<<<ctx->sm_count * per_sm, kTraceThreads, 0, stream>>>(ctx->view(), d_rays, d_queue, d_queue_count, max_depth, d_mat_transp, n_mat, d_out, d_work_counter);
+	if(ctx->two_level) k_trace_tshadow_queue<true><<<ctx->sm_count * per_sm, kTraceThreads, 0, stream>>>(Y4Bvh8{}, ctx->view2(), d_rays, d_queue, d_queue_count, max_depth, d_mat_transp, n_mat, d_out, d_work_counter);
+	else k_trace_tshadow_queue<false><<<ctx->sm_count * per_sm, kTraceThreads, 0, stream>>>(ctx->view(), Y4Scene2{}, d_rays, d_queue, d_queue_count, max_depth, d_mat_transp, n_mat, d_out, d_work_counter);
 	Y4_CUDA(ctx, cudaGetLastError());
 	ctx->stats.kernel_launches++;
 	return Y4GPU_OK;
@@ -632,14 +639,14 @@ int y4_launch_tshadow_wave(y4gpu_ctx *ctx, const Y4Ray *d_rays, Y4Hit *d_out, co
 
 int y4_launch_tshadow(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out)
 {
-	if(ctx->two_level) { ctx->err = "filtered transparent shadows are not available on a two-level (instanced) scene"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(n == 0) return Y4GPU_OK;
 	cudaStream_t st = ctx->stream;
 	Y4_CUDA(ctx, cudaMemsetAsync(ctx->d_work_counter, 0, sizeof(uint32_t), st));
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
 	const uint64_t want = (n + kTraceThreads - 1) / kTraceThreads;
 	const uint64_t full = (uint64_t) ctx->sm_count * 4;
-	k_trace_tshadow<<<(int) (want < full ? want : full), kTraceThreads, 0, st>>>(ctx->view(), d_rays, n, max_depth, d_mat_transp, n_mat, d_out, ctx->d_work_counter, 0);
+	if(ctx->two_level) k_trace_tshadow<true><<<(int) (want < full ? want : full), kTraceThreads, 0, st>>>(Y4Bvh8{}, ctx->view2(), d_rays, n, max_depth, d_mat_transp, n_mat, d_out, ctx->d_work_counter, 0);
+	else k_trace_tshadow<false><<<(int) (want < full ? want : full), kTraceThreads, 0, st>>>(ctx->view(), Y4Scene2{}, d_rays, n, max_depth, d_mat_transp, n_mat, d_out, ctx->d_work_counter, 0);
 	Y4_CUDA(ctx, cudaGetLastError());
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
 	ctx->stats.kernel_launches++;
@@ -665,11 +672,12 @@ int y4_launch_trace_on(y4gpu_ctx *ctx, int kind, const Y4Ray *d_rays, uint64_t n
 int y4_launch_tshadow_on(y4gpu_ctx *ctx, const Y4Ray *d_rays, uint64_t n, int max_depth, const float *d_mat_transp, uint32_t n_mat, y4gpu_tshit *d_out,
                          bool inner, unsigned long long *d_work_counter, cudaStream_t stream)
 {
-	if(ctx->two_level) { ctx->err = "filtered transparent shadows are not available on a two-level (instanced) scene"; return Y4GPU_ERR_UNSUPPORTED; }
 	if(n == 0) return Y4GPU_OK;
 	const uint64_t want = (n + kTraceThreads - 1) / kTraceThreads;
 	const uint64_t full = (uint64_t) ctx->sm_count * 4;
-	k_trace_tshadow<<<(int) (want < full ? want : full), kTraceThreads, 0, stream>>>(ctx->view(), d_rays, n, max_depth, d_mat_transp, n_mat, d_out,
+if(ctx->two_level) k_trace_tshadow<true><<<(int) (want < full ? want : full), kTraceThreads, 0, stream>>>(Y4Bvh8{}, ctx->view2(), d_rays, n, max_depth, d_mat_transp, n_mat, d_out,
+	                                                                                   reinterpret_cast<uint32_t *>(d_work_counter), inner ? 1 : 0);
+	else k_trace_tshadow<false><<<(int) (want < full ? want : full), kTraceThreads, 0, stream>>>(ctx->view(), Y4Scene2{}, d_rays, n, max_depth, d_mat_transp, n_mat, d_out,
 	                                                                                   reinterpret_cast<uint32_t *>(d_work_counter), inner ? 1 : 0);
 	Y4_CUDA(ctx, cudaGetLastError());
 	return Y4GPU_OK;

@@ -401,8 +401,11 @@ Y4_HD bool y4_inst_tri(const Y4Inst &in, const Y4TriObj &tr, const V3 o, const V
 #define Y4_INST_NONE 0xffffffffu
 // One ray through the two-level structure.  Stack entries: node groups (top byte of .y non-zero), pending leaf groups (top byte
 // zero) and the marker {0xffffffff, 0} under which the top-level state waits while an instance is walked.
+// filt / filt_mat / n_filt / max_depth: the transparent-shadow query with filter colours (as y4_trace_ray); without them a
+// transparent-shadow ray ends at its first blocker.
 template<int KIND>
-Y4_HD void y4_trace_ray2(const Y4Scene2 &sc, const Y4PreparedRay &ray, Y4Hit &hit, uint2 *stack, Y4TraceStats *stats)
+Y4_HD void y4_trace_ray2(const Y4Scene2 &sc, const Y4PreparedRay &ray, Y4Hit &hit, uint2 *stack, Y4TraceStats *stats,
+                         uint32_t *filt = nullptr, uint32_t *filt_mat = nullptr, int *n_filt = nullptr, int max_depth = 0)
 {
 	hit.t = 0.f; hit.bu = 0.f; hit.bv = 0.f; hit.prim = -1;
 	if(sc.n_inst == 0 || !(ray.t_hi > ray.t_lo)) return;
@@ -478,6 +481,14 @@ Y4_HD void y4_trace_ray2(const Y4Scene2 &sc, const Y4PreparedRay &ray, Y4Hit &hi
 				if(!(tr.flags & vis_bit)) continue;
 				const uint32_t prim = in.first_prim + tr.prim_local;
 				if(!y4_accept_t<KIND>(t, ray.t_lo, t_hi, prim, hit.prim)) continue;
+				if(KIND == Y4_TRACE_TSHADOW && filt && (tr.flags & Y4_TRI_TRANSPARENT))
+				{
+					// a transparent blocker: each distinct primitive filters once, more than max_depth of them shadow the point
+					bool seen = false;
+					for(int k = 0; k < *n_filt; ++k) seen = seen || (filt[k] == prim);
+					if(seen) continue;
+					if(*n_filt < max_depth) { filt[*n_filt] = prim; filt_mat[(*n_filt)++] = tr.flags >> Y4_TRI_MAT_SHIFT; continue; }
+				}
 				hit.t = t; hit.bu = u; hit.bv = v; hit.prim = (int32_t) prim;
 				if(KIND == Y4_TRACE_CLOSEST) t_hi = t;
 				else { done = true; break; }

@@ -77,9 +77,9 @@ class Interface:
         self._cur_mat: Optional[str] = None
         self._next_id = 0
         self.accelerator: Optional[AcceleratorB200] = None
-        # instanced objects (addInstance): "auto" keeps the base meshes once on the device (two-level BVH8, results identical to the
-        # flattened scene) whenever the scene has instances and nothing needs the flat arrays (filtered transparent shadows do);
-        # False always flattens like the reference's scene does.  Env Y4GPU_INSTANCING=0/1 overrides.
+        # instanced objects (addInstance): "auto" / True keep the base meshes once on the device (two-level BVH8, results identical
+        # to the flattened scene) whenever the scene has instances; False always flattens like the reference's scene does.
+        # Env Y4GPU_INSTANCING=0/1 overrides.
         self.device_instancing = "auto"
         self.film_buffers = None  # optional (weights, rgba) torch CUDA tensors installed by the caller
         self._pinned_film = None
@@ -747,12 +747,7 @@ class Interface:
             mode = env not in ("0", "false", "")
         if mode is False or not any(o.instance_of for o in self.objects.values()):
             return False
-        if mode is True:
-            return True
-        # auto: filtered transparent shadows walk the flat tree only
-        integ = next(iter(self.integrators.values()), {}) if self.integrators else {}
-        transp = any(float(m.get("transparency", 0.0)) > 0.00001 for m in self.materials.values())
-        return not (bool(integ.get("transpShad", False)) and transp)
+        return True
 
     @property
     def sharded(self) -> bool:

@@ -101,7 +101,7 @@ int emu_build_trace(const float *verts, const uint32_t *flags, int n, const floa
 		Y4TraceStats s{0, 0};
 		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray<Y4_TRACE_CLOSEST>(bvh, pr, hits[i], stack, &s, filt, filt_mat, &n_filt, 0);
 		else if(kind == Y4_TRACE_SHADOW) y4_trace_ray<Y4_TRACE_SHADOW>(bvh, pr, hits[i], stack, &s, filt, filt_mat, &n_filt, 0);
-		else y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, hits[i], stack, &s, filt, filt_mat, &n_filt, 8);
+		else { y4_trace_ray<Y4_TRACE_TSHADOW>(bvh, pr, hits[i], stack, &s, filt, filt_mat, &n_filt, 8); hits[i].bu = (float) n_filt; }
 		sn += s.nodes; st += s.tris;
 	}
 	if(stats_out) { stats_out[0] = sn; stats_out[1] = st; }
@@ -191,7 +191,7 @@ int emu_build_trace2(const float *mesh_verts, const uint32_t *mesh_flags, const 
 		Y4TraceStats s{0, 0};
 		if(kind == Y4_TRACE_CLOSEST) y4_trace_ray2<Y4_TRACE_CLOSEST>(sc, pr, hits[i], stack, &s);
 		else if(kind == Y4_TRACE_SHADOW) y4_trace_ray2<Y4_TRACE_SHADOW>(sc, pr, hits[i], stack, &s);
-		else y4_trace_ray2<Y4_TRACE_TSHADOW>(sc, pr, hits[i], stack, &s);
+		else { uint32_t filt[16], filt_mat[16]; int n_filt = 0; y4_trace_ray2<Y4_TRACE_TSHADOW>(sc, pr, hits[i], stack, &s, filt, filt_mat, &n_filt, 8); hits[i].bu = (float) n_filt; }
 		sn += s.nodes; st += s.tris;
 	}
 	if(stats_out) { stats_out[0] = sn; stats_out[1] = st; }

@@ -211,8 +211,22 @@ def test_two_level_instanced_scene_equals_the_flattened_upload():
     a_two.intersect(rays, counted=True)
     st = a_two.stats()
     assert st["nodes_visited"] > len(rays) and st["tris_tested"] > 0           # visit counters (the roofline's algorithmic bytes)
-    with pytest.raises(Exception):
-        a_two.isShadowedTransparent(rays[:16], 4, np.ones((1, 3), np.float32))      # filtered shadows: flat scenes only
+    # filtered transparent shadows (intersectTs): two meshes transparent, one colour per material
+    from libyafaray_b200 import _lib
+    vis = _lib.TRI_VIS_CLOSEST | _lib.TRI_VIS_SHADOW | _lib.TRI_VIS_TSHADOW
+    mesh_flags = [np.full(len(m), vis | (_lib.TRI_TRANSPARENT if i in (0, 2) else 0) | (i << _lib.TRI_MAT_SHIFT), np.uint32) for i, m in enumerate(meshes)]
+    flat_flags = np.concatenate([mesh_flags[mi] for mi, _ in inst])
+    mt = np.random.default_rng(3).uniform(0.2, 0.9, (len(meshes), 3)).astype(np.float32)
+    b_flat, b_two = AcceleratorB200(flat, flags=flat_flags, leaf_max=3), AcceleratorB200.from_instances(meshes, inst, mesh_flags=mesh_flags, leaf_max=3)
+    ts_rays = helpers.city_rays(100000, seed=9)
+    ts_rays[:, 7] = 2.5                     # segments: many end inside the city after crossing only transparent walls
+    for depth in (1, 3, 8):
+        s1, s2 = b_flat.isShadowedTransparent(ts_rays, depth, mt), b_two.isShadowedTransparent(ts_rays, depth, mt)
+        assert np.array_equal(s1["prim"] >= 0, s2["prim"] >= 0)
+        lit = s1["prim"] < 0
+        # the layers multiply in the order the walk meets them: the products agree to fp32 rounding
+        assert np.allclose(s1["filter"][lit], s2["filter"][lit], rtol=1e-6, atol=0)
+        assert (s1["filter"][lit] < 0.999).any()
     # a collapsed instance cannot be walked in object space: refused (the Interface then uploads the flattened scene); an instance
     # of an empty mesh owns no primitives and changes nothing
     with pytest.raises(Exception, match="singular"):

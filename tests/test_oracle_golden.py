@@ -130,3 +130,14 @@ def test_two_level_traversal_equals_the_flattened_scene_bit_for_bit():
         o1, _, _ = helpers.emu_build_trace(flat, rays, 1, leaf_max=3)
         o2, _, _ = helpers.emu_build_trace2(meshes, inst, rays, 1)
         assert np.array_equal(o1["prim"] >= 0, o2["prim"] >= 0)
+    # transparent shadows (intersectTs): two of the meshes are transparent; same verdict and the same number of filtering layers
+    from libyafaray_b200 import _lib
+    mesh_flags = [np.full(len(m), _lib.TRI_VIS_CLOSEST | _lib.TRI_VIS_SHADOW | _lib.TRI_VIS_TSHADOW | (_lib.TRI_TRANSPARENT if i in (0, 2) else 0) | (i << _lib.TRI_MAT_SHIFT), np.uint32)
+                  for i, m in enumerate(meshes)]
+    flat_flags = np.concatenate([mesh_flags[mi] for mi, _ in inst])
+    rays = helpers.city_rays(20000, seed=9)
+    t1, _, _ = helpers.emu_build_trace(flat, rays, 2, leaf_max=3, flags=flat_flags)
+    t2, _, _ = helpers.emu_build_trace2(meshes, inst, rays, 2, mesh_flags=mesh_flags)
+    lit = t1["prim"] < 0           # (a shadowed ray stops at its opaque blocker: how many layers it met before depends on the walk order)
+    assert np.array_equal(t1["prim"] >= 0, t2["prim"] >= 0) and np.array_equal(t1["bu"][lit], t2["bu"][lit])
+    assert (t1["bu"][lit] > 0).mean() > 0.02 and (t1["bu"][lit] > 1).any()

@@ -251,6 +251,24 @@ def test_c4_instanced_city_vs_reference_golden(key, cfg, instancing):
     assert frac <= 1e-2
 
 
+def test_filtered_transparent_shadows_on_a_two_level_scene_equal_the_flattened_scene():
+    """transpShad with transparent instanced buildings: the filter-colour traversal walks instances too."""
+    from make_golden import PT_GOLDEN_CITY
+    cfg = PT_GOLDEN_CITY[sorted(PT_GOLDEN_CITY)[0]]
+    films = []
+    for instancing in (False, True):
+        yi = _gpu(**cfg)
+        yi.device_instancing = instancing
+        yi.materials["wall0"].update(transparency=0.6, transmit_filter=0.8)
+        yi.materials["wall2"].update(transparency=0.4)
+        for integ in yi.integrators.values():
+            integ.update(transpShad=True, shadowDepth=4)
+        films.append(yi.render())
+        assert yi._assembled["two_level"] == instancing
+    assert np.abs(films[0] - films[1]).max() <= 2e-6 * max(1.0, float(films[0].max()))
+    assert films[0][..., :3].mean() > 0.01
+
+
 def test_russian_roulette_default_configuration_statistics():
     """The integrator's DEFAULT configuration (russian_roulette_min_bounces = 0) is the documented non-sample-exact case: the
     reference draws roulette numbers from a rand()-seeded generator, the device from a per-path hash.  Both are unbiased, so the
