@@ -314,11 +314,33 @@ __global__ void __launch_bounds__(128) k_collapse(Y4BinTree bt, int leaf_max, co
 	y4_collapse_item(bt, leaf_max, items[2 * i], items[2 * i + 1], verts, tri_flags, out);
 }
 
+// Scratch arena of a series of small builds (the bottom-level trees of a two-level scene): one allocation serves every
+// temporary of every build instead of ~20 cudaMalloc / cudaFree pairs per mesh.  Set per host thread around the series.
+struct Arena
+{
+	char *base = nullptr; size_t cap = 0, used = 0;
+	void *take(size_t bytes)
+	{
+		const size_t at = (used + 255) & ~(size_t) 255;
+		if(!base || at + bytes > cap) return nullptr;
+		used = at + bytes;
+		return base + at;
+	}
+};
+thread_local Arena *t_arena = nullptr;
+
 template<typename T> struct DevBuf
 {
 	T *p = nullptr;
-	~DevBuf() { if(p) cudaFree(p); }
-	cudaError_t alloc(size_t n) { return cudaMalloc(&p, (n ? n : 1) * sizeof(T)); }
+	bool owned = true;
+	~DevBuf() { if(p && owned) cudaFree(p); }
+	cudaError_t alloc(size_t n)
+	{
+		const size_t bytes = (n ? n : 1) * sizeof(T);
+		if(t_arena) { p = static_cast<T *>(t_arena->take(bytes)); if(p) { owned = false; return cudaSuccess; } }
+		owned = true;
+		return cudaMalloc(&p, bytes);
+	}
 };
 
 } // namespace
@@ -329,6 +351,7 @@ struct Y4Built
 {
 	Y4U4 *nodes = nullptr; Y4Tri *tris = nullptr;
 	uint64_t n_nodes = 0;
+	bool placed = false;               // nodes / tris were given by the caller (room for n nodes and n leaf records): no allocation, no shrink
 	int levels = 0, morton_used = 0;
 	float raw[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 };
@@ -439,10 +462,14 @@ static int build_core(y4gpu_ctx *ctx, const float *d_verts, const uint32_t *d_fl
 
 	// collapse into BVH8
 	const uint64_t max_nodes = (uint64_t) n;   // every wide node below the root owns >= 1 binary internal node
-	Y4U4 *nodes = nullptr; Y4Tri *tris = nullptr;
-	Y4_CUDA(ctx, cudaMalloc(&nodes, max_nodes * Y4_NODE_WORDS * sizeof(Y4U4)));
-	if(cudaMalloc(&tris, (size_t) n * sizeof(Y4Tri)) != cudaSuccess) { cudaFree(nodes); ctx->err = "cudaMalloc tris failed"; return Y4GPU_ERR_CUDA; }
-	res.nodes = nodes; res.tris = tris;
+	Y4U4 *nodes = res.nodes; Y4Tri *tris = res.tris;
+	if(!res.placed)
+	{
+		nodes = nullptr; tris = nullptr;
+		Y4_CUDA(ctx, cudaMalloc(&nodes, max_nodes * Y4_NODE_WORDS * sizeof(Y4U4)));
+		if(cudaMalloc(&tris, (size_t) n * sizeof(Y4Tri)) != cudaSuccess) { cudaFree(nodes); ctx->err = "cudaMalloc tris failed"; return Y4GPU_ERR_CUDA; }
+		res.nodes = nodes; res.tris = tris;
+	}
 	Y4_CUDA(ctx, items_a.alloc(2ull * n + 2)); Y4_CUDA(ctx, items_b.alloc(2ull * n + 2));
 	const uint32_t init_counters[4] = {1u, 0u, 0u, 0u};   // node_counter, tri_counter, next_count, pad
 	Y4_CUDA(ctx, cudaMemcpyAsync(counters.p, init_counters, sizeof(init_counters), cudaMemcpyHostToDevice, st));
@@ -474,7 +501,7 @@ static int build_core(y4gpu_ctx *ctx, const float *d_verts, const uint32_t *d_fl
 	if(fin[1] != (uint32_t) n) { ctx->err = "collapse lost triangles"; return Y4GPU_ERR_CUDA; }
 	res.n_nodes = fin[0];
 	// shrink the node array to its final size so only the live BVH stays resident
-	if(res.n_nodes < max_nodes)
+	if(!res.placed && res.n_nodes < max_nodes)
 	{
 		Y4U4 *small = nullptr;
 		if(cudaMalloc(&small, res.n_nodes * Y4_NODE_WORDS * sizeof(Y4U4)) == cudaSuccess)
@@ -629,39 +656,54 @@ int y4_build_two_level(y4gpu_ctx *ctx, int leaf_max)
 	if(n_inst == 0 || ctx->n_tri == 0) { ctx->built = true; return Y4GPU_OK; }
 	if(leaf_max < 1 || leaf_max > 3) { ctx->err = "leaf_max must be 1..3"; return Y4GPU_ERR_ARG; }
 	Y4_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
-	// bottom level: every mesh on its own, then pooled (node / leaf indices stay mesh-relative: the instance carries the offsets)
-	std::vector<Y4Built> blas(n_mesh);
+	// bottom level: every mesh on its own, built straight into the pooled arrays (node / leaf indices stay mesh-relative: the
+	// instance carries the offsets).  One scratch arena sized for the largest mesh serves the temporaries of all builds.
 	std::vector<uint32_t> node_off(n_mesh, 0u), tri_off(n_mesh, 0u);
 	std::vector<float> bmax(n_mesh, 0.f);
-	uint64_t nodes_total = 0, tris_total = 0;
+	uint64_t nodes_total = 0, tris_total = 0, tris_all = ctx->mesh_first[n_mesh], n_max = 0;
+	for(size_t i = 0; i < n_mesh; ++i) n_max = std::max<uint64_t>(n_max, ctx->mesh_first[i + 1] - ctx->mesh_first[i]);
 	int blas_levels = 0, rc = Y4GPU_OK;
+	Y4U4 *pool_nodes = nullptr;
+	if(cudaMalloc(&pool_nodes, (tris_all ? tris_all : 1) * Y4_NODE_WORDS * sizeof(Y4U4)) != cudaSuccess || cudaMalloc(&ctx->d_blas_tris, (tris_all ? tris_all : 1) * sizeof(Y4TriObj)) != cudaSuccess)
+	{
+		cudaFree(pool_nodes); ctx->err = "cudaMalloc of the pooled bottom-level trees failed"; return Y4GPU_ERR_CUDA;
+	}
+	Arena arena;
+	size_t sort_tmp_bytes = 0;
+	{
+		cub::DoubleBuffer<uint64_t> qk; cub::DoubleBuffer<uint32_t> qv;
+		cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp_bytes, qk, qv, (int) n_max, 0, 63, st);
+	}
+	arena.cap = (size_t) n_max * 200 + sort_tmp_bytes + (64u << 10);
+	if(cudaMalloc(&arena.base, arena.cap) != cudaSuccess) { arena.base = nullptr; arena.cap = 0; cudaGetLastError(); }      // (falls back to per-buffer allocations)
+	t_arena = &arena;
 	for(size_t i = 0; i < n_mesh && !rc; ++i)
 	{
 		const uint64_t first = ctx->mesh_first[i], n = ctx->mesh_first[i + 1] - first;
 		if(n == 0) continue;
-		rc = build_core(ctx, ctx->d_mesh_verts + 9ull * first, ctx->d_mesh_flags ? ctx->d_mesh_flags + first : nullptr, (int) n, leaf_max, blas[i]);
+		arena.used = 0;
+		Y4Built b;
+		b.placed = true; b.nodes = pool_nodes + nodes_total * Y4_NODE_WORDS; b.tris = reinterpret_cast<Y4Tri *>(ctx->d_blas_tris + tris_total);
+		rc = build_core(ctx, ctx->d_mesh_verts + 9ull * first, ctx->d_mesh_flags ? ctx->d_mesh_flags + first : nullptr, (int) n, leaf_max, b);
 		if(rc) break;
-		k_blas_leaves<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(blas[i].tris, (int) n, ctx->d_mesh_verts + 9ull * first);
+		k_blas_leaves<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(b.tris, (int) n, ctx->d_mesh_verts + 9ull * first);
 		node_off[i] = (uint32_t) nodes_total; tri_off[i] = (uint32_t) tris_total;
-		nodes_total += blas[i].n_nodes; tris_total += n;
-		if(blas[i].levels > blas_levels) blas_levels = blas[i].levels;
-		for(int k = 0; k < 6; ++k) bmax[i] = fmaxf(bmax[i], fabsf(blas[i].raw[k]));
+		nodes_total += b.n_nodes; tris_total += n;
+		if(b.levels > blas_levels) blas_levels = b.levels;
+		for(int k = 0; k < 6; ++k) bmax[i] = fmaxf(bmax[i], fabsf(b.raw[k]));
 	}
-	auto free_blas = [&]() { for(Y4Built &b : blas) { cudaFree(b.nodes); cudaFree(b.tris); b.nodes = nullptr; b.tris = nullptr; } };
-	if(rc) { free_blas(); return rc; }
-	if(cudaMalloc(&ctx->d_blas_nodes, nodes_total * Y4_NODE_WORDS * sizeof(Y4U4)) != cudaSuccess || cudaMalloc(&ctx->d_blas_tris, tris_total * sizeof(Y4TriObj)) != cudaSuccess)
+	t_arena = nullptr;
+	cudaStreamSynchronize(st);
+	cudaFree(arena.base);
+	if(rc) { cudaFree(pool_nodes); return rc; }
+	// the node pool was sized for the worst case (one node per triangle): keep the live part only
+	if(cudaMalloc(&ctx->d_blas_nodes, (nodes_total ? nodes_total : 1) * Y4_NODE_WORDS * sizeof(Y4U4)) != cudaSuccess) { cudaGetLastError(); ctx->d_blas_nodes = pool_nodes; }
+	else
 	{
-		free_blas(); ctx->err = "cudaMalloc of the pooled bottom-level trees failed"; return Y4GPU_ERR_CUDA;
+		Y4_CUDA(ctx, cudaMemcpyAsync(ctx->d_blas_nodes, pool_nodes, nodes_total * Y4_NODE_WORDS * sizeof(Y4U4), cudaMemcpyDeviceToDevice, st));
+		Y4_CUDA(ctx, cudaStreamSynchronize(st));
+		cudaFree(pool_nodes);
 	}
-	for(size_t i = 0; i < n_mesh; ++i)
-	{
-		const uint64_t n = ctx->mesh_first[i + 1] - ctx->mesh_first[i];
-		if(n == 0) continue;
-		cudaMemcpyAsync(ctx->d_blas_nodes + (size_t) node_off[i] * Y4_NODE_WORDS, blas[i].nodes, blas[i].n_nodes * Y4_NODE_WORDS * sizeof(Y4U4), cudaMemcpyDeviceToDevice, st);
-		cudaMemcpyAsync(ctx->d_blas_tris + tri_off[i], blas[i].tris, n * sizeof(Y4TriObj), cudaMemcpyDeviceToDevice, st);
-	}
-	Y4_CUDA(ctx, cudaStreamSynchronize(st));
-	free_blas();
 	ctx->n_blas_nodes = nodes_total; ctx->n_base_tris = tris_total;
 	// instances: offsets of their mesh, inverse transforms; device copy; exact world boxes as proxy triangles; top-level tree
 	for(Y4Inst &in : ctx->h_inst)
