@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(kTraceThreads) k_trace_tshadow_queue(Y4Bvh8 bv
 // COUNT: visit counters as in k_trace (visit[0] nodes of either level, visit[1] triangle tests, visit[2] live rays); an instance
 // entry -- its 48-byte top-level leaf record + the 128-byte instance record -- is counted as two nodes (160 B).
 template<int KIND, bool QUEUE, bool COUNT>
-__global__ void __launch_bounds__(kTraceThreads, 2) k_trace2(Y4Scene2 sc, const Y4Ray *__restrict__ rays, uint64_t n, Y4Hit *__restrict__ out,
+__global__ void __launch_bounds__(kTraceThreads, 3) k_trace2(Y4Scene2 sc, const Y4Ray *__restrict__ rays, uint64_t n, Y4Hit *__restrict__ out,
                                                              unsigned long long *__restrict__ work_counter, unsigned long long *__restrict__ visit, int fetch_threshold,
                                                              const uint32_t *__restrict__ queue, const uint32_t *__restrict__ queue_count)
 {
