@@ -262,8 +262,12 @@ typedef struct y4gpu_pt_layer     /* one `layer` node together with the `texture
 enum { Y4GPU_LIGHT_POINT = 0, Y4GPU_LIGHT_AREA = 1, Y4GPU_LIGHT_DIRECTIONAL = 2, Y4GPU_LIGHT_SUN = 3, Y4GPU_LIGHT_SPHERE = 4, Y4GPU_LIGHT_SPOT = 5,
        Y4GPU_LIGHT_OBJECT = 6,     /* `objectlight` / `meshlight` (light_object_light.cc): the triangles of a mesh emit */
        Y4GPU_LIGHT_BACKGROUND = 7,
-       Y4GPU_LIGHT_SPOT_SOFT = 8 };    /* `spotlight` with soft_shadows = true (light_spot.cc:106-144, 199-246): a sampled light; the
-                                      fields of Y4GPU_LIGHT_SPOT plus samples and radius = `shadow_fuzzyness` */   /* `bglight` (light_background.cc): the IBL light a `constant` / `gradientback` background creates with
+       Y4GPU_LIGHT_SPOT_SOFT = 8,
+       Y4GPU_LIGHT_PORTAL = 9 };    /* `spotlight` with soft_shadows = true (light_spot.cc:106-144, 199-246): a sampled light; the
+                                      fields of Y4GPU_LIGHT_SPOT plus samples and radius = `shadow_fuzzyness`
+                                      Y4GPU_LIGHT_PORTAL: `bgPortalLight` (light_background_portal.cc): the triangles of a mesh (object_tris /
+                                      object_n_tris as for Y4GPU_LIGHT_OBJECT, single sided) emit the background of y4gpu_pt_params seen
+                                      through them, times `power`; the mesh itself must not be uploaded (the reference makes it invisible) */   /* `bglight` (light_background.cc): the IBL light a `constant` / `gradientback` background creates with
                                       ibl = true; it importance-samples the background of y4gpu_pt_params (tabulated on 360 latitude rows).
                                       samples = `ibl_samples`, cast_shadows, double_sided = `abs_intersect`; put it where its name
                                       ("constantBackground_bgLight" / "GradientBackground_bgLight") sorts among the lights */

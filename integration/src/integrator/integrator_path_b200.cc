@@ -368,7 +368,7 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 				l.type = Y4GPU_LIGHT_AREA; l.samples = get<int>(p, "samples", 4);
 				put3(l.from, getVec(p, "corner", Vec3{0.f})); put3(l.point1, getVec(p, "point1", Vec3{0.f})); put3(l.point2, getVec(p, "point2", Vec3{0.f}));
 			}
-			else if(type == "objectlight" || type == "meshlight")
+			else if(type == "objectlight" || type == "meshlight" || type == "bgPortalLight")
 			{
 				const Object *obj = scene.getObject(getStr(p, "object_name"));
 				if(!obj || obj->numPrimitives() == 0) unsupported("objectlight '" + kv.first + "': object_name must name a mesh with triangles");
@@ -382,6 +382,7 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 					for(int k = 0; k < 3; ++k) { const Point3 v = face->getVertex(k); tv.push_back(v.x()); tv.push_back(v.y()); tv.push_back(v.z()); }
 				}
 				l.type = Y4GPU_LIGHT_OBJECT; l.samples = get<int>(p, "samples", 4); l.double_sided = get<bool>(p, "double_sided", false);
+				if(type == "bgPortalLight") { l.type = Y4GPU_LIGHT_PORTAL; l.double_sided = 0; if(!background_) unsupported("bgPortalLight without a background"); }
 				l.object_n_tris = (uint32_t) (tv.size() / 9);
 			}
 			else if(type == "bglight")      // created by a background's factory with ibl = true (background_constant.cc:58-69); checked against the rendered background below
@@ -392,7 +393,7 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 			else unsupported("light type '" + type + "'");
 			lights.push_back(l);
 		}
-		for(size_t i = 0, k = 0; i < lights.size(); ++i) if(lights[i].type == Y4GPU_LIGHT_OBJECT) lights[i].object_tris = light_tris[k++].data();
+		for(size_t i = 0, k = 0; i < lights.size(); ++i) if(lights[i].type == Y4GPU_LIGHT_OBJECT || lights[i].type == Y4GPU_LIGHT_PORTAL) lights[i].object_tris = light_tris[k++].data();
 		// ---- background ----------------------------------------------------------------------------------------------------------
 		bool rendered_background_has_ibl = false;
 		std::string ibl_light_name;

@@ -112,7 +112,7 @@ class PtAaNoise(C.Structure):
 
 
 MAT_SHINYDIFFUSE, MAT_LIGHT, MAT_MIRROR, MAT_GLASS = 0, 1, 2, 3
-LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT, LIGHT_OBJECT, LIGHT_BACKGROUND, LIGHT_SPOT_SOFT = 0, 1, 2, 3, 4, 5, 6, 7, 8
+LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT, LIGHT_OBJECT, LIGHT_BACKGROUND, LIGHT_SPOT_SOFT, LIGHT_PORTAL = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
 CAMERA_TYPES = {"perspective": 0, "architect": 1, "orthographic": 2, "equirectangular": 3}
 BOKEH_TYPES = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}

@@ -573,7 +573,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		if(mats[i].layer_count < 0 || (mats[i].layer_count > 0 && (mats[i].layer_first < 0 || !ctx->pt || (uint32_t) (mats[i].layer_first + mats[i].layer_count) > ctx->pt->n_layers)))
 		{ ctx->err = "material refers to layers that were not set (call y4gpu_pt_set_textures first)"; return Y4GPU_ERR_ARG; }
 	for(uint32_t i = 0; i < n_light; ++i)
-		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_SPOT_SOFT) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
+		if(lights[i].type < Y4GPU_LIGHT_POINT || lights[i].type > Y4GPU_LIGHT_PORTAL) { ctx->err = "unsupported light type"; return Y4GPU_ERR_UNSUPPORTED; }
 	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
 	if(!ctx->pt) ctx->pt = new Y4Pt;
 	if(const char *e = getenv("Y4GPU_PT_MIN_BLOCKS")) ctx->pt->stage_min_blocks = atoi(e);
@@ -620,7 +620,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		chain_mats = chain_mats || mats[m].type == Y4GPU_MAT_MIRROR || mats[m].type == Y4GPU_MAT_GLASS || (mats[m].type == Y4GPU_MAT_SHINYDIFFUSE && (mats[m].specular_reflect > 0.00001f || mats[m].transparency > 0.00001f));
 	if(chain_mats && sc.no_recursive) { ctx->err = "no_recursive with mirror materials / specular_reflect is not supported"; return Y4GPU_ERR_UNSUPPORTED; }
 	// object lights need the general kernel variant as well (not the ray levels)
-	for(uint32_t l = 0; l < n_light; ++l) if((lights[l].type == Y4GPU_LIGHT_OBJECT || lights[l].type == Y4GPU_LIGHT_BACKGROUND || lights[l].type == Y4GPU_LIGHT_SPOT_SOFT) && !sc.has_specular) sc.has_specular = 1;
+	for(uint32_t l = 0; l < n_light; ++l) if((lights[l].type == Y4GPU_LIGHT_OBJECT || lights[l].type == Y4GPU_LIGHT_BACKGROUND || lights[l].type == Y4GPU_LIGHT_SPOT_SOFT || lights[l].type == Y4GPU_LIGHT_PORTAL) && !sc.has_specular) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
@@ -638,7 +638,8 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	for(uint32_t i = 0; i < n_light; ++i)
 	{
 		pt->h_lights[i] = derive_light(lights[i]);
-		if(lights[i].type == Y4GPU_LIGHT_OBJECT)
+		if(lights[i].type == Y4GPU_LIGHT_PORTAL) derive_light_background(pt->h_lights[i], *params);
+		if(lights[i].type == Y4GPU_LIGHT_OBJECT || lights[i].type == Y4GPU_LIGHT_PORTAL)
 		{
 			// the light's own copy of its mesh: vertices, geometric normals, area cdf (ObjectLight::initIs) in one device block
 			const uint32_t n = lights[i].object_n_tris;

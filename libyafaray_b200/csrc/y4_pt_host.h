@@ -235,6 +235,11 @@ inline Y4PtLight derive_light(const y4gpu_pt_light &l)
 		return o;
 	}
 	const float pi_f = (float) 3.14159265358979323846264338327950288L;
+	if(l.type == Y4GPU_LIGHT_PORTAL)                      // BackgroundPortalLight ctor: power_; area / cdf: derive_object_light; background: derive_light_background
+	{
+		o.power = l.power; o.double_sided = 0; o.obj_n = (int) l.object_n_tris;
+		return o;
+	}
 	if(l.type == Y4GPU_LIGHT_OBJECT)                      // ObjectLight::factory: color * (float) power * num_pi; area / cdf: derive_object_light
 	{
 		o.color = c3(pi_f * (l.power * l.color[0]), pi_f * (l.power * l.color[1]), pi_f * (l.power * l.color[2]));
@@ -300,6 +305,15 @@ inline float derive_pdf1d(const float *func, int n, std::vector<float> &cdf)
 	return integral;
 }
 
+// the background a background / portal light evaluates (Background::eval): a copy of the render parameters' description
+inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p)
+{
+	o.bg_gradient = p.background_gradient;
+	o.bg_col = c3(p.background[0], p.background[1], p.background[2]);
+	o.bg_gz = c3(p.bg_gradient[0][0], p.bg_gradient[0][1], p.bg_gradient[0][2]); o.bg_gh = c3(p.bg_gradient[1][0], p.bg_gradient[1][1], p.bg_gradient[1][2]);
+	o.bg_sz = c3(p.bg_gradient[2][0], p.bg_gradient[2][1], p.bg_gradient[2][2]); o.bg_sh = c3(p.bg_gradient[3][0], p.bg_gradient[3][1], p.bg_gradient[3][2]);
+}
+
 // BackgroundLight::init (light_background.cc:46-75): the background's energy * sin(theta) on 360 latitude rows of
 // 16 + (int)(sin(theta) * 704) columns, a Pdf1D per row and one over the row integrals.  The caller stores the arrays
 // where the light's pointers can reach them; the background's own description is copied into the light for eval().
@@ -307,10 +321,7 @@ inline void derive_background_light(Y4PtLight &o, const y4gpu_pt_light &l, const
                                     std::vector<int> &off, std::vector<float> &func, std::vector<float> &cdf, std::vector<float> &inv_int)
 {
 	o.bg_abs_inter = l.double_sided;
-	o.bg_gradient = p.background_gradient;
-	o.bg_col = c3(p.background[0], p.background[1], p.background[2]);
-	o.bg_gz = c3(p.bg_gradient[0][0], p.bg_gradient[0][1], p.bg_gradient[0][2]); o.bg_gh = c3(p.bg_gradient[1][0], p.bg_gradient[1][1], p.bg_gradient[1][2]);
-	o.bg_sz = c3(p.bg_gradient[2][0], p.bg_gradient[2][1], p.bg_gradient[2][2]); o.bg_sh = c3(p.bg_gradient[3][0], p.bg_gradient[3][1], p.bg_gradient[3][2]);
+	derive_light_background(o, p);
 	const int nv = 360, max_u = 720, min_u = 16;
 	o.bg_nv = nv;
 	off.clear(); func.clear(); cdf.clear(); inv_int.clear();

@@ -517,9 +517,9 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 		ls.dir = ldir; ls.tmax = dist; ls.col = L.color;
 		return true;
 	}
-	if(GENERAL && L.type == Y4GPU_LIGHT_OBJECT)
+	if(GENERAL && (L.type == Y4GPU_LIGHT_OBJECT || L.type == Y4GPU_LIGHT_PORTAL))
 	{
-		// ObjectLight::sampleSurface (light_object_light.cc:87-105): Pdf1D::dSample = lower_bound on the cdf, the sample number
+		// ObjectLight::sampleSurface / BackgroundPortalLight::sampleSurface (same code) (light_object_light.cc:87-105): Pdf1D::dSample = lower_bound on the cdf, the sample number
 		// re-stretched inside the chosen triangle's cdf step, TrianglePrimitive::sample (primitive_triangle.cc:228-234)
 		const int n = L.obj_n;
 		int idx;
@@ -553,6 +553,12 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 			else return false;
 		}
 		const float amc = xmul(L.area, cos_angle);
+		if(L.type == Y4GPU_LIGHT_PORTAL)                    // BackgroundPortalLight::illumSample (light_background_portal.cc:127-157)
+		{
+			ls.pdf = (float) (xdmul((Y4_WIDE) dist_sqr, Y4_PI) / (Y4_WIDE) amc);
+			ls.dir = ldir; ls.tmax = dist; ls.col = cscale(y4_bg_eval(L, ldir), L.power);
+			return true;
+		}
 		ls.pdf = (float) (xdmul((Y4_WIDE) dist_sqr, Y4_PI) / (Y4_WIDE) (amc == 0.f ? 1e-8f : amc));
 		ls.dir = ldir; ls.tmax = dist; ls.col = L.color;
 		return true;
@@ -617,6 +623,10 @@ Y4_HD bool y4_light_illum_sample(const Y4PtLight &L, const V3 from, float s1, fl
 template<bool GENERAL = true>
 Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, float tmin, float &t, C3 &col, float &ipdf)
 {
+	// BackgroundPortalLight::intersect (light_background_portal.cc:176-191) asks the light's own kd-tree, which was built AFTER
+	// init() made the mesh invisible (:79-80): the tree's closest-hit query skips invisible primitives, so the call never hits and
+	// the BSDF-sampling half of the MIS estimate contributes nothing (the light-sampling half keeps its MIS weight).  Reproduced.
+	if(GENERAL && L.type == Y4GPU_LIGHT_PORTAL) return false;
 	if(GENERAL && L.type == Y4GPU_LIGHT_OBJECT)
 	{
 		// ObjectLight::intersect (:183-201): closest hit of the light's own accelerator over [ray.tmin_, inf) -- here a loop over its

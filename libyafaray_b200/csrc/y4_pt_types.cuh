@@ -106,10 +106,11 @@ struct Y4PtLight
 	const int *bg_off;          // [bg_nv + 2]
 	const float *bg_func, *bg_cdf, *bg_inv_int;     // bg_inv_int[y] = Pdf1D::invIntegral() of row y
 	int bg_gradient; C3 bg_col, bg_gz, bg_gh, bg_sz, bg_sh;     // the background itself (Background::eval)
+	float power;                // portal light: bg_->eval(dir) * power_
 };
 // Light::diracLight() / Light::canIntersect() of the supported lights (include/light/light_*.h)
 Y4_HD bool y4_light_dirac(int type) { return type == Y4GPU_LIGHT_POINT || type == Y4GPU_LIGHT_DIRECTIONAL || type == Y4GPU_LIGHT_SPOT; }
-Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN || type == Y4GPU_LIGHT_OBJECT || type == Y4GPU_LIGHT_BACKGROUND || type == Y4GPU_LIGHT_SPOT_SOFT; }
+Y4_HD bool y4_light_can_intersect(int type) { return type == Y4GPU_LIGHT_AREA || type == Y4GPU_LIGHT_SUN || type == Y4GPU_LIGHT_OBJECT || type == Y4GPU_LIGHT_BACKGROUND || type == Y4GPU_LIGHT_SPOT_SOFT || type == Y4GPU_LIGHT_PORTAL; }
 
 #define Y4_PT_MAX_LIGHTS 64
 #define Y4_FILTER_TABLE 16

@@ -256,7 +256,7 @@ class Interface:
 
     def createLight(self, name):
         p = dict(self.params)
-        if p.get("type") not in ("pointlight", "arealight", "directional", "sunlight", "spherelight", "spotlight", "objectlight", "meshlight"):
+        if p.get("type") not in ("pointlight", "arealight", "directional", "sunlight", "spherelight", "spotlight", "objectlight", "meshlight", "bgPortalLight"):
             raise Y4Error(f"light type '{p.get('type')}' is not supported by the GPU back end")
         self.lights[name] = p
         return True
@@ -445,11 +445,13 @@ class Interface:
             base_cache[base.name] = (v, idx, f, nn, oc, uv)
             return base_cache[base.name]
 
+        # BackgroundPortalLight::init makes its mesh invisible (light_background_portal.cc:79): it only shapes the light
+        portal_meshes = {str(p.get("object_name", "")) for p in self.lights.values() if p.get("type") == "bgPortalLight"}
         for name in sorted(self.objects):
             o = self.objects[name]
             base = self.objects[o.instance_of] if o.instance_of else o
             vis_o, sh_o = VIS.get(base.visibility, VIS["normal"])
-            if (not vis_o and not sh_o) or o.is_base:
+            if (not vis_o and not sh_o) or o.is_base or base.name in portal_meshes:
                 continue
             if not base.tris:
                 continue
@@ -615,13 +617,17 @@ class Interface:
                     l.type, l.samples, l.radius = _lib.LIGHT_SPOT_SOFT, int(p.get("samples", 8)), float(p.get("shadowFuzzyness", 1.0))
                 l.from_[:] = p.get("from", (0.0, 0.0, 0.0))
                 l.point1[:] = p.get("to", (0.0, 0.0, -1.0))
-            elif p["type"] in ("objectlight", "meshlight"):     # ObjectLight::factory (light_object_light.cc:222-253)
+            elif p["type"] in ("objectlight", "meshlight", "bgPortalLight"):     # ObjectLight::factory (light_object_light.cc:222-253)
                 o = self.objects.get(str(p.get("object_name", "")))
                 if o is None or o.instance_of or not o.tris:
-                    raise Y4Error(f"objectlight '{n}': object_name must name a mesh with triangles")
+                    raise Y4Error(f"{p['type']} '{n}': object_name must name a mesh with triangles")
                 ov = np.asarray(o.verts, np.float64).astype(np.float32)[np.asarray(o.tris, np.int64)].reshape(-1, 9)
                 self._light_tris.append(np.ascontiguousarray(ov))          # kept alive until the scene is uploaded
                 l.type, l.samples, l.double_sided = _lib.LIGHT_OBJECT, int(p.get("samples", 4)), int(p.get("double_sided", False))
+                if p["type"] == "bgPortalLight":     # BackgroundPortalLight::factory (light_background_portal.cc:207-237): the background seen through the mesh
+                    if bg is None:
+                        raise Y4Error(f"bgPortalLight '{n}' needs a background")
+                    l.type, l.double_sided = _lib.LIGHT_PORTAL, 0
                 l.object_n_tris, l.object_tris = len(ov), self._light_tris[-1].ctypes.data
             elif p["type"] == "bglight":           # BackgroundLight::factory (light_background.cc:200-224); created by createBackground
                 if p["_background"] != rp.get("background_name", ""):

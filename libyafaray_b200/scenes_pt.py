@@ -84,12 +84,13 @@ def _uv_sphere(centre, radius, nu, nv):
 def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, light_samples=1, filter_type="box",
                 aa_pixelwidth=1.5, threads=1, accelerator="yafaray-kdtree-original", rr_min_bounces=None, point_light=False,
                 oren_nayar=False, integrator="pathtracing", aperture=0.0, dof_distance=0.0, extra_lights=(), bokeh=None, smooth_sphere=None, camera_extra=None,
-                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None, mesh_light=None, glass=None, box_lift=0.0, lamp=True):
+                mirror=None, integrator_extra=None, background=(0.0, 0.0, 0.0), glow=0.0, shiny=None, render_extra=None, pane=None, mesh_light=None, glass=None, box_lift=0.0, lamp=True, portal=None):
     """C2: Cornell box, ceiling area light (+ emitting quad via object_name), diffuse walls and two boxes.
     extra_lights: any of "sun", "directional", "directional_finite", "sphere", "spot" shining in through the open front.
     mirror: {"objects": subset of ("tall", "short", "back", "left", "sphere"), "color": rgb, "reflect": r} -> those objects get a
     `mirror` material; integrator_extra: integrator parameters set after the defaults (raydepth, caustic_type, ...).
-    lamp=False: no ceiling lamp at all (the box is then lit through its open front, e.g. by a background with ibl=True)."""
+    lamp=False: no ceiling lamp at all (the box is then lit through its open front, e.g. by a background with ibl=True).
+    portal: power of a `bgPortalLight` whose mesh closes the open front (the background seen through it lights the box)."""
     white, red, green = (0.73, 0.73, 0.73), (0.65, 0.05, 0.05), (0.12, 0.45, 0.15)
     extra = {"diffuse_brdf": "oren_nayar", "sigma": 0.3} if oren_nayar else {}
     extra.update(shiny or {})          # shiny: shinydiffusemat parameters of all three wall materials (specular_reflect, mirror_color, fresnel_effect, IOR)
@@ -154,6 +155,9 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     if pane:
         v, t = _quad((0.1, 0.05, 0.45), (0.9, 0.05, 0.45), (0.9, 0.8, 0.45), (0.1, 0.8, 0.45))
         _mesh(api, "j_pane", "pane", v, t)
+    if portal is not None:              # across the open front, facing into the box (the light makes the mesh itself invisible)
+        v, t = _quad((0.0, 0.0, 0.0), (1.0, 0.0, 0.0), (1.0, 1.0, 0.0), (0.0, 1.0, 0.0))
+        _mesh(api, "p_portal", "white", v, t)
     api.endGeometry()
 
     api.paramsClearAll()
@@ -180,6 +184,13 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         api.paramsSetString("object_name", "h_lamp")
     if lamp:
         api.createLight("lamp")
+    if portal is not None:
+        api.paramsClearAll()
+        api.paramsSetString("type", "bgPortalLight")
+        api.paramsSetString("object_name", "p_portal")
+        api.paramsSetFloat("power", float(portal))
+        api.paramsSetInt("samples", light_samples)
+        api.createLight("portal")
     for kind in extra_lights:
         api.paramsClearAll()
         if kind == "sun":                               # wide cone so that several samples differ visibly

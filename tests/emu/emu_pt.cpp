@@ -132,7 +132,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	}
 	if(sc.has_specular == 3 && params->transp_background) return -3;
 	// object lights need the general kernel variant as well (not the ray levels)
-	for(uint32_t l = 0; l < n_light; ++l) if((lights[l].type == Y4GPU_LIGHT_OBJECT || lights[l].type == Y4GPU_LIGHT_BACKGROUND || lights[l].type == Y4GPU_LIGHT_SPOT_SOFT) && !sc.has_specular) sc.has_specular = 1;
+	for(uint32_t l = 0; l < n_light; ++l) if((lights[l].type == Y4GPU_LIGHT_OBJECT || lights[l].type == Y4GPU_LIGHT_BACKGROUND || lights[l].type == Y4GPU_LIGHT_SPOT_SOFT || lights[l].type == Y4GPU_LIGHT_PORTAL) && !sc.has_specular) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
@@ -147,7 +147,8 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	static std::vector<std::vector<float>> obj_cdf, obj_tris; static std::vector<std::vector<float4>> obj_ng;     // object lights' mesh copies
 	obj_cdf.assign(n_light, {}); obj_tris.assign(n_light, {}); obj_ng.assign(n_light, {});
 	for(uint32_t i = 0; i < n_light; ++i) { hl[i] = derive_light(lights[i]);
-		if(lights[i].type == Y4GPU_LIGHT_OBJECT)
+		if(lights[i].type == Y4GPU_LIGHT_PORTAL) derive_light_background(hl[i], *params);
+		if(lights[i].type == Y4GPU_LIGHT_OBJECT || lights[i].type == Y4GPU_LIGHT_PORTAL)
 		{
 			obj_tris[i].assign(lights[i].object_tris, lights[i].object_tris + 9ull * lights[i].object_n_tris);
 			derive_object_light(hl[i], obj_tris[i].data(), lights[i].object_n_tris, obj_cdf[i], obj_ng[i]);

@@ -13,6 +13,7 @@ UNMODIFIED reference (oracle/_ref), committed so that the GPU box can check them
   pt_ibl.npz        <- Cornell box lit by an IBL background light (PT_GOLDEN_IBL), deterministic mode
   pt_shiny2.npz     <- Cornell box with a shinydiffusemat sheet that is mirror AND transparent (PT_GOLDEN_SHINY2), deterministic mode
   pt_spot_soft.npz  <- Cornell box lit by a spotlight with soft_shadows = true (PT_GOLDEN_SPOT_SOFT), deterministic mode
+  pt_portal.npz     <- Cornell box lit through a bgPortalLight across its opening (PT_GOLDEN_PORTAL), deterministic mode
   pt_rr.npz         <- Cornell box with the integrator's default Russian roulette (russian_roulette_min_bounces = 0), 1024 spp
 
 Run from the repo root:  python tests/golden/make_golden_large.py [soup|city]
@@ -160,6 +161,28 @@ def make_spot_soft():
     np.savez_compressed(os.path.join(HERE, "pt_spot_soft.npz"), **out)
 
 
+# bgPortalLight: a mesh across the box's opening emits the background seen through it (light_background_portal.cc) -> pt_portal.npz
+_SKY_PLAIN = dict(type="gradientback", horizon_color=(1.0, 0.9, 0.7, 1.0), zenith_color=(0.2, 0.4, 1.0, 1.0), horizon_ground_color=(0.5, 0.4, 0.3, 1.0),
+                  zenith_ground_color=(0.1, 0.1, 0.1, 1.0), power=2.0)
+PT_GOLDEN_PORTAL = {
+    "portal_gradient_path": dict(width=96, height=54, spp=3, bounces=4, lamp=False, portal=1.5, background=_SKY_PLAIN),
+    "portal_constant_direct": dict(width=80, height=45, spp=2, bounces=3, integrator="directlighting", lamp=False, portal=2.0, light_samples=3,
+                                   background=dict(type="constant", color=(0.8, 0.9, 1.0, 1.0), power=1.2)),
+    "portal_direct_with_lamp_gauss": dict(width=80, height=45, spp=2, bounces=3, integrator="directlighting", portal=1.0, light_samples=2, filter_type="gauss",
+                                          background=_SKY_PLAIN, smooth_sphere=30.0),
+}
+
+
+def make_portal():
+    out = {}
+    for key, kw in PT_GOLDEN_PORTAL.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print(key, float(out[key][..., :3].mean()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_portal.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -188,6 +211,8 @@ if __name__ == "__main__":
         make_shiny2()
     if "spot_soft" in what:
         make_spot_soft()
+    if "portal" in what:
+        make_portal()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

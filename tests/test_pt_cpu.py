@@ -441,6 +441,22 @@ def test_soft_spot_light_vs_golden_reference_render(key):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+@pytest.mark.parametrize("key", ["portal_gradient_path", "portal_constant_direct", "portal_direct_with_lamp_gauss"])
+def test_background_portal_light_vs_golden_reference_render(key):
+    """bgPortalLight: the triangles of a mesh emit the background seen through them (sampled like an object light, single sided,
+    colour = Background::eval(direction) * power); the mesh itself becomes invisible."""
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_PORTAL
+    ref = np.load(os.path.join(GOLD, "pt_portal.npz"))[key]
+    a = _assemble(**PT_GOLDEN_PORTAL[key])
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 def _shiny2_cfgs():
     sys.path.insert(0, GOLD)
     from make_golden_large import PT_GOLDEN_SHINY2
