@@ -37,15 +37,20 @@ class AcceleratorB200 final : public Accelerator
 		const std::vector<const Material *> &materialTable() const { return materials_; }   // index = material id in the triangle flag words
 		// triangle `i` of the device == primitives()[i]: its mesh face and (for instances) the object-to-world matrix
 		static const FacePrimitive *faceOf(const Primitive *primitive, const Matrix4 **obj_to_world);
+		// re-upload when an object's visibility changed after the build (lights are initialised after the accelerator: scene.cc:218-220)
+		bool refreshVisibility() const;
 
 	private:
 		AcceleratorB200(Logger &logger, y4gpu_ctx *ctx, const std::vector<const Primitive *> &primitives, std::vector<const Material *> materials, std::vector<float> mat_transparency, const Bound &bound)
 			: Accelerator(logger), ctx_(ctx), primitives_(primitives), materials_(std::move(materials)), mat_transparency_(std::move(mat_transparency)), bound_(bound) { }
+		static bool uploadScene(Logger &logger, y4gpu_ctx *ctx, const std::vector<const Primitive *> &primitives, std::vector<const Material *> &materials,
+		                        std::vector<float> &mat_transparency, bool &ts_varying, std::vector<uint32_t> &flags_out);
 		y4gpu_ctx *ctx_ = nullptr;
 		std::vector<const Primitive *> primitives_;     // the factory's vector is a temporary: keep a copy (index -> pointer)
-		std::vector<const Material *> materials_;
-		std::vector<float> mat_transparency_;           // [n_mat * 3] Material::getTransparency colour of the transparent materials
-		bool ts_varying_ = false;                       // some transparent material's colour is not one constant: intersectTs refuses
+		mutable std::vector<const Material *> materials_;
+		mutable std::vector<float> mat_transparency_;   // [n_mat * 3] Material::getTransparency colour of the transparent materials
+		mutable std::vector<uint32_t> flags_;           // the flag words as uploaded
+		mutable bool ts_varying_ = false;               // some transparent material's colour is not one constant: intersectTs refuses
 		mutable std::atomic<bool> ts_error_logged_{false};
 		Bound bound_;
 };

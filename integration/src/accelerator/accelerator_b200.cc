@@ -28,21 +28,16 @@ const FacePrimitive *AcceleratorB200::faceOf(const Primitive *primitive, const M
 	return dynamic_cast<const FacePrimitive *>(base);
 }
 
-const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<const Primitive *> &primitives, const ParamMap &params)
+// Everything between "a context exists" and "the scene is resident": flag words, material table, geometry upload (two-level when
+// the list is made of instance runs) and build.  Used by the factory and by refreshVisibility().
+bool AcceleratorB200::uploadScene(Logger &logger, y4gpu_ctx *ctx, const std::vector<const Primitive *> &primitives, std::vector<const Material *> &materials,
+                                  std::vector<float> &mat_transparency, bool &ts_varying, std::vector<uint32_t> &flags_out)
 {
-	int device = 0;
-	params.getParam("b200_device", device);
-	if(const char *e = getenv("Y4GPU_DEVICE")) device = atoi(e);
-	y4gpu_ctx *ctx = nullptr;
-	if(y4gpu_create(device, &ctx) != Y4GPU_OK)
-	{
-		logger.logError("AcceleratorB200: ", y4gpu_last_error(nullptr));
-		return nullptr;
-	}
 	const size_t n = primitives.size();
 	std::vector<float> verts(n * 9);
-	std::vector<uint32_t> flags(n);
-	std::vector<const Material *> materials;
+	std::vector<uint32_t> &flags = flags_out;
+	flags.assign(n, 0u);
+	materials.clear();
 	std::unordered_map<const Material *, uint32_t> material_index;
 	std::vector<const Primitive *> first_with_material;
 	for(size_t i = 0; i < n; ++i)
@@ -52,8 +47,7 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 		if(!face || face->getVerticesIndices().size() != 3)
 		{
 			logger.logError("AcceleratorB200: primitive ", i, " is not a triangle (only triangle meshes and their instances are supported)");
-			y4gpu_destroy(ctx);
-			return nullptr;
+			return false;
 		}
 		// world-space vertices exactly as the reference computes them for every test (FacePrimitive::getVertex: Matrix4 * Point3)
 		for(int k = 0; k < 3; ++k)
@@ -82,8 +76,8 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 	}
 	// Material::getTransparency of the transparent materials, evaluated by the reference's own code on one surface point.  The
 	// device multiplies one colour per material, so a colour that varies over the surface cannot be reproduced: refuse it.
-	std::vector<float> mat_transparency(materials.size() * 3, 0.f);
-	bool ts_varying = false;
+	mat_transparency.assign(materials.size() * 3, 0.f);
+	ts_varying = false;
 	for(size_t mi = 0; mi < materials.size(); ++mi)
 	{
 		if(!materials[mi] || !materials[mi]->isTransparent()) continue;
@@ -181,6 +175,57 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 	if(!two_level && (y4gpu_upload_triangles(ctx, verts.data(), flags.data(), n) != Y4GPU_OK || y4gpu_build(ctx, nullptr) != Y4GPU_OK))
 	{
 		logger.logError("AcceleratorB200: ", y4gpu_last_error(ctx));
+		return false;
+	}
+	return true;
+}
+
+// visibility word of one primitive: the matrix of accelerator_kdtree.cc:733-737 (closest), :869-873 (shadow), :1022 (transparent shadow)
+static uint32_t visibilityBits(const Primitive *primitive)
+{
+	const Material *mat = primitive->getMaterial();
+	const Visibility vo = primitive->getVisibility(), vm = mat ? mat->getVisibility() : Visibility::NormalVisible;
+	const bool seen_o = vo == Visibility::NormalVisible || vo == Visibility::VisibleNoShadows, shad_o = vo == Visibility::NormalVisible || vo == Visibility::InvisibleShadowsOnly;
+	const bool seen_m = vm == Visibility::NormalVisible || vm == Visibility::VisibleNoShadows, shad_m = vm == Visibility::NormalVisible || vm == Visibility::InvisibleShadowsOnly;
+	uint32_t w = 0;
+	if(seen_o && seen_m) w |= Y4GPU_TRI_VIS_CLOSEST;
+	if(shad_o && shad_m) w |= Y4GPU_TRI_VIS_SHADOW;
+	if(shad_m) w |= Y4GPU_TRI_VIS_TSHADOW;
+	return w;
+}
+
+// The reference reads visibilities at query time; the device bakes them into the flag words at upload.  Scene::render builds the
+// accelerator BEFORE it initialises the lights (scene.cc:218-220), and a light may change an object's visibility there
+// (BackgroundPortalLight::init hides its mesh): the integrator calls this from preprocess() and the scene goes up again if a
+// visibility changed in between.
+bool AcceleratorB200::refreshVisibility() const
+{
+	const uint32_t mask = Y4GPU_TRI_VIS_CLOSEST | Y4GPU_TRI_VIS_SHADOW | Y4GPU_TRI_VIS_TSHADOW;
+	bool changed = false;
+	for(size_t i = 0; i < primitives_.size() && !changed; ++i) changed = (flags_[i] & mask) != visibilityBits(primitives_[i]);
+	if(!changed) return true;
+	logger_.logInfo("AcceleratorB200: object visibilities changed after the build (a light hid its mesh): uploading the scene again");
+	return uploadScene(logger_, ctx_, primitives_, materials_, mat_transparency_, ts_varying_, flags_);
+}
+
+const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<const Primitive *> &primitives, const ParamMap &params)
+{
+	int device = 0;
+	params.getParam("b200_device", device);
+	if(const char *e = getenv("Y4GPU_DEVICE")) device = atoi(e);
+	y4gpu_ctx *ctx = nullptr;
+	if(y4gpu_create(device, &ctx) != Y4GPU_OK)
+	{
+		logger.logError("AcceleratorB200: ", y4gpu_last_error(nullptr));
+		return nullptr;
+	}
+	std::vector<const Material *> materials;
+	std::vector<float> mat_transparency;
+	std::vector<uint32_t> flags;
+	bool ts_varying = false;
+	const size_t n = primitives.size();
+	if(!uploadScene(logger, ctx, primitives, materials, mat_transparency, ts_varying, flags))
+	{
 		y4gpu_destroy(ctx);
 		return nullptr;
 	}
@@ -191,6 +236,7 @@ const Accelerator *AcceleratorB200::factory(Logger &logger, const std::vector<co
 	logger.logInfo("AcceleratorB200: ", n, " triangles, ", st.n_nodes, " BVH8 nodes in ", st.bvh_levels, " levels, built in ", st.build_ms, " ms on the GPU");
 	auto *acc = new AcceleratorB200(logger, ctx, primitives, std::move(materials), std::move(mat_transparency), Bound{{b[0], b[1], b[2]}, {b[3], b[4], b[5]}});
 	acc->ts_varying_ = ts_varying;
+	acc->flags_ = std::move(flags);
 	return acc;
 }
 

@@ -123,6 +123,7 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 	accel_ = dynamic_cast<const AcceleratorB200 *>(accelerator_);
 	if(!accel_) { logger_.logError(getName(), ": needs scene_accelerator = yafaray-b200-bvh8 (the scene was built with another accelerator)"); return false; }
 	ctx_ = accel_->context();
+	if(!accel_->refreshVisibility()) { logger_.logError(getName(), ": ", y4gpu_last_error(ctx_)); return false; }
 	const B200SceneParams &rec = scene.getB200Params();
 	const ParamMap &rp = rec.render;
 	try
