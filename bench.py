@@ -91,7 +91,7 @@ def pt_config_dict(args, world=1):
         "path_samples": 1, "russian_roulette": "off (min_bounces = bounces: the reference's deterministic mode)",
         "samples_per_step_per_gpu": args.pt_width * args.pt_height * spp_gpu,
         "scaling": args.scaling,
-        "l2": "no flush needed: the path state of the wavefronts in flight (2 x 4 Mi paths x 380 B = 3 GB) is far larger than the 126 MB L2",
+        "l2": "no flush needed: the path state of the wavefronts in flight (2 x 8 Mi pixel-samples x ~1 KB = 17 GB) is far larger than the 126 MB L2",
         "sharding": "AA-pass samples s mod N per GPU, scene + BVH replicated, one NCCL all-reduce of the pass film (5 floats/pixel) per step",
         "secondary": "`raybatch`: " + ("C5 (configs[4]) 50M-triangle soup, 2 x 16 Mi ray batches" if args.workload == "c5" else "C3 (configs[2]) 1M-triangle sphere, 3 x 16 Mi ray batches per GPU per step"),
     }
@@ -650,6 +650,8 @@ def pt_arm(args, env):
         else:
             scenes_pt.cornell_box(yi, width=W, height=H, spp=spp_step, bounces=bounces, accelerator=ACCELERATOR_TYPE)
         yi.render_params["b200_profile"] = profile
+        if os.environ.get("Y4_BENCH_WAVE"):          # (tuning runs: pixel-samples per wavefront, default 2^23)
+            yi.render_params["b200_wave_size"] = int(os.environ["Y4_BENCH_WAVE"])
         return yi
 
     # N > 1: the product's sharded mode (Interface with a comm): every rank splats into its pass film, ONE NCCL all-reduce of

@@ -320,7 +320,7 @@ typedef struct y4gpu_pt_params
 	int32_t min_raydist_auto; float min_raydist;        /* adv_auto_min_raydist_enabled / adv_min_raydist_value */
 	uint32_t base_sampling_offset;                      /* adv_base_sampling_offset + 100000 * adv_computer_node */
 	uint32_t rr_seed;             /* seed of the per-path Russian-roulette hash (the reference uses rand()) */
-	uint32_t wave_size;           /* pixel-samples processed per wavefront (0 = default 2^22) */
+	uint32_t wave_size;           /* pixel-samples processed per wavefront (0 = default 2^23) */
 	int32_t profile;              /* 1: time every kernel class with CUDA events and count BVH visits (slower; for the roofline) */
 	int32_t transp_shadows;       /* integrator transpShad: shadow rays take the intersectTs rules (material visibility only,
 	                                 tmin <= t < t_max; accelerator_kdtree.cc:911-1061): opaque blockers shadow, transparent

@@ -937,7 +937,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 			d_list = pt->d_pixel_list;
 		}
 	}
-	uint32_t wave_size = pt->params.wave_size ? pt->params.wave_size : (1u << 22);
+	uint32_t wave_size = pt->params.wave_size ? pt->params.wave_size : (1u << 23);      // 8 Mi pixel-samples: ~1 KB of state per slot, two wavefronts in flight = 17 GB of the 180 (profiles/r2_v10_sweep_wave.log)
 	if(total < wave_size) wave_size = (uint32_t) (total ? total : 1);
 	const bool prof = pt->params.profile != 0;
 	// lanes: consecutive waves alternate between two streams (profile mode times kernels one by one: single lane)
