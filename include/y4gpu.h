@@ -289,9 +289,13 @@ typedef struct y4gpu_pt_light
 	const float *object_tris;     /* objectlight: their world-space vertices [object_n_tris * 9], in the mesh's face order (host memory, copied) */
 } y4gpu_pt_light;
 
-enum { Y4GPU_CAM_PERSPECTIVE = 0, Y4GPU_CAM_ARCHITECT = 1, Y4GPU_CAM_ORTHOGRAPHIC = 2, Y4GPU_CAM_EQUIRECTANGULAR = 3 };
+enum { Y4GPU_CAM_PERSPECTIVE = 0, Y4GPU_CAM_ARCHITECT = 1, Y4GPU_CAM_ORTHOGRAPHIC = 2, Y4GPU_CAM_EQUIRECTANGULAR = 3, Y4GPU_CAM_ANGULAR = 4 };
+/* AngularCamera::Projection (camera_angular.h): the `projection` string of the angular camera's factory (camera_angular.cc:108-112) */
+enum { Y4GPU_ANGULAR_EQUIDISTANT = 0, Y4GPU_ANGULAR_ORTHOGRAPHIC = 1, Y4GPU_ANGULAR_STEREOGRAPHIC = 2, Y4GPU_ANGULAR_EQUISOLID_ANGLE = 3,
+       Y4GPU_ANGULAR_RECTILINEAR = 4 };
 typedef struct y4gpu_pt_camera    /* camera parameters: `perspective` (camera_perspective.cc:182-220), `architect` (camera_architect.cc),
-                                     `orthographic` (camera_orthographic.cc: `scale` travels in `focal`), `equirectangular` */
+                                     `orthographic` (camera_orthographic.cc: `scale` travels in `focal`), `equirectangular`,
+                                     `angular` (camera_angular.cc:80-117) */
 {
 	float from[3], to[3], up[3];
 	int32_t resx, resy;
@@ -300,6 +304,11 @@ typedef struct y4gpu_pt_camera    /* camera parameters: `perspective` (camera_pe
 	int32_t bokeh_bias;           /* 0 uniform, 1 center, 2 edge */
 	float bokeh_rotation;         /* degrees (polygonal lens shapes) */
 	int32_t type;                 /* Y4GPU_CAM_* */
+	/* angular camera only (camera_angular.cc:84-112): the factory's double parameters as given; the radians, the focal length of
+	   the projection (libm tan / FAST_TRIG sin) and max_radius = max_angle / angle are derived on the host like the constructor does */
+	double angle_degrees, max_angle_degrees;
+	int32_t circular, mirrored;   /* circular: pixels beyond max_radius get no ray (black, alpha 1); mirrored: vright negated */
+	int32_t projection;           /* Y4GPU_ANGULAR_* */
 } y4gpu_pt_camera;
 
 enum { Y4GPU_FILTER_BOX = 0, Y4GPU_FILTER_GAUSS = 1, Y4GPU_FILTER_MITCHELL = 2, Y4GPU_FILTER_LANCZOS = 3 };
@@ -400,6 +409,12 @@ int y4gpu_pt_read_film(y4gpu_ctx *ctx, float *weights, float *rgba);
  * imageFilmLoadAllInFolder leave in weights_ and the Combined layer before a resumed render (imagefilm.cc:827-1018). */
 int y4gpu_pt_write_film(y4gpu_ctx *ctx, const float *weights, const float *rgba);
 int y4gpu_pt_get_stats(const y4gpu_ctx *ctx, y4gpu_pt_stats *out);
+
+/* Self-check of the device's fp32 inverse trigonometric functions (csrc/y4_libm.cuh), which stand in for the C library calls of
+ * the reference (std::atan2 / std::atan / std::asin in AngularCamera::shootRay, camera_angular.cc:66-71; std::acos in
+ * Texture::sphereMap, math.h:253-259).  out[i] = f(a[i]) for fn 0 atanf, 1 asinf, 2 acosf; out[i] = atan2f(a[i], b[i]) for fn 3.
+ * Host or device pointers; the caller compares with its own libm, bit for bit (tests/test_libm.py). */
+int y4gpu_libm_eval(y4gpu_ctx *ctx, int fn, const float *a, const float *b, float *out, uint64_t n);
 
 #ifdef __cplusplus
 }

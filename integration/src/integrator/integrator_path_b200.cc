@@ -86,7 +86,9 @@ std::vector<ChainEntry> diffuseChain(const std::string &mat_name, const ParamMap
 	return chain;
 }
 
-const std::map<std::string, int> kCameraTypes{{"perspective", 0}, {"architect", 1}, {"orthographic", 2}, {"equirectangular", 3}};
+const std::map<std::string, int> kCameraTypes{{"perspective", 0}, {"architect", 1}, {"orthographic", 2}, {"equirectangular", 3}, {"angular", 4}};
+const std::map<std::string, int> kAngularProjections{{"orthographic", Y4GPU_ANGULAR_ORTHOGRAPHIC}, {"stereographic", Y4GPU_ANGULAR_STEREOGRAPHIC},
+                                                     {"equisolid_angle", Y4GPU_ANGULAR_EQUISOLID_ANGLE}, {"rectilinear", Y4GPU_ANGULAR_RECTILINEAR}};
 const std::map<std::string, int> kBokehTypes{{"disk1", 0}, {"disk2", 1}, {"triangle", 3}, {"square", 4}, {"pentagon", 5}, {"hexagon", 6}, {"ring", 7}};
 const std::map<std::string, int> kBokehBias{{"uniform", 0}, {"center", 1}, {"edge", 2}};
 const std::map<std::string, int> kClip{{"extend", 0}, {"clip", 1}, {"clipcube", 2}, {"repeat", 3}, {"checker", 4}};
@@ -166,7 +168,15 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 		if(cam.type == Y4GPU_CAM_ORTHOGRAPHIC) cam.focal = get<float>(cp, "scale", 1.f);
 		if(cam.type == Y4GPU_CAM_PERSPECTIVE || cam.type == Y4GPU_CAM_ARCHITECT) { cam.aperture = get<float>(cp, "aperture", 0.f); cam.dof_distance = get<float>(cp, "dof_distance", 0.f); }
 		cam.near_clip = get<float>(cp, "nearClip", 0.f);
-		cam.far_clip = get<float>(cp, "farClip", cam.type == Y4GPU_CAM_EQUIRECTANGULAR ? -1.0e38f : -1.f);
+		cam.far_clip = get<float>(cp, "farClip", (cam.type == Y4GPU_CAM_EQUIRECTANGULAR || cam.type == Y4GPU_CAM_ANGULAR) ? -1.0e38f : -1.f);
+		if(cam.type == Y4GPU_CAM_ANGULAR)                // AngularCamera::factory (camera_angular.cc:80-117)
+		{
+			cam.angle_degrees = get<double>(cp, "angle", 90.0);
+			cam.max_angle_degrees = get<double>(cp, "max_angle", cam.angle_degrees);
+			cam.circular = get<bool>(cp, "circular", true) ? 1 : 0;
+			cam.mirrored = get<bool>(cp, "mirrored", false) ? 1 : 0;
+			cam.projection = lookup(kAngularProjections, getStr(cp, "projection", ""), Y4GPU_ANGULAR_EQUIDISTANT);
+		}
 		cam.bokeh_type = lookup(kBokehTypes, getStr(cp, "bokeh_type", "disk1"), 0);
 		cam.bokeh_bias = lookup(kBokehBias, getStr(cp, "bokeh_bias", "uniform"), 0);
 		cam.bokeh_rotation = get<float>(cp, "bokeh_rotation", 0.f);

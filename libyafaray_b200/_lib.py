@@ -82,7 +82,9 @@ class PtCamera(C.Structure):
     _fields_ = [("from_", C.c_float * 3), ("to", C.c_float * 3), ("up", C.c_float * 3), ("resx", C.c_int32), ("resy", C.c_int32),
                 ("aspect_ratio", C.c_float), ("focal", C.c_float), ("aperture", C.c_float), ("dof_distance", C.c_float),
                 ("near_clip", C.c_float), ("far_clip", C.c_float), ("bokeh_type", C.c_int32), ("bokeh_bias", C.c_int32),
-                ("bokeh_rotation", C.c_float), ("type", C.c_int32)]  # fmt: skip
+                ("bokeh_rotation", C.c_float), ("type", C.c_int32),
+                ("angle_degrees", C.c_double), ("max_angle_degrees", C.c_double), ("circular", C.c_int32), ("mirrored", C.c_int32),
+                ("projection", C.c_int32)]  # fmt: skip
 
 
 class PtParams(C.Structure):
@@ -114,7 +116,8 @@ class PtAaNoise(C.Structure):
 MAT_SHINYDIFFUSE, MAT_LIGHT, MAT_MIRROR, MAT_GLASS = 0, 1, 2, 3
 LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT, LIGHT_OBJECT, LIGHT_BACKGROUND, LIGHT_SPOT_SOFT, LIGHT_PORTAL = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
-CAMERA_TYPES = {"perspective": 0, "architect": 1, "orthographic": 2, "equirectangular": 3}
+CAMERA_TYPES = {"perspective": 0, "architect": 1, "orthographic": 2, "equirectangular": 3, "angular": 4}
+ANGULAR_PROJECTIONS = {"equidistant": 0, "orthographic": 1, "stereographic": 2, "equisolid_angle": 3, "rectilinear": 4}
 BOKEH_TYPES = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}
 BOKEH_BIAS = {"uniform": 0, "center": 1, "edge": 2}
 CLIP_MODES = {"extend": 0, "clip": 1, "clipcube": 2, "repeat": 3, "checker": 4}
@@ -142,7 +145,7 @@ EXPORTED = [
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow", "y4gpu_trace_tshadow_inner", "y4gpu_trace_noalloc",
     "y4gpu_set_ray_sort", "y4gpu_get_stats", "y4gpu_synchronize",
     "y4gpu_pt_set_textures", "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
-    "y4gpu_pt_read_film", "y4gpu_pt_write_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass",
+    "y4gpu_pt_read_film", "y4gpu_pt_write_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass", "y4gpu_libm_eval",
 ]  # fmt: skip
 
 
@@ -203,6 +206,8 @@ def lib() -> C.CDLL:
     L.y4gpu_pt_render_pass.restype = i32
     L.y4gpu_pt_next_pass.argtypes = [vp, vp, vp, vp, C.POINTER(vp), C.POINTER(C.c_uint64)]
     L.y4gpu_pt_next_pass.restype = i32
+    L.y4gpu_libm_eval.argtypes = [vp, i32, vp, vp, vp, u64]
+    L.y4gpu_libm_eval.restype = i32
     L.y4gpu_pt_read_film.argtypes = [vp, vp, vp]
     L.y4gpu_pt_read_film.restype = i32
     L.y4gpu_pt_write_film.argtypes = [vp, vp, vp]

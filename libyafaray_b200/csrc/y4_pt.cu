@@ -116,6 +116,16 @@ __global__ void __launch_bounds__(kPtThreads) k_pt_gen(const __grid_constant__ Y
 	}
 }
 
+// y4gpu_libm_eval: the inverse trigonometric restatements on the device (self-check against the host's libm)
+__global__ void k_libm_eval(int fn, const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ out, uint64_t n)
+{
+	for(uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x)
+	{
+		const float x = a[i];
+		out[i] = fn == 0 ? y4_libm_atanf(x) : (fn == 1 ? y4_libm_asinf(x) : (fn == 2 ? y4_libm_acosf(x) : y4_libm_atan2f(x, b[i])));
+	}
+}
+
 template<int STAGE, int MINB, bool SPEC>
 __global__ void __launch_bounds__(kPtThreads, MINB) k_pt_stage(const __grid_constant__ Y4PtScene sc, Y4PtWave W, Y4PtPass ps, StageArgs a, StageQueues Q)
 {
@@ -782,6 +792,28 @@ int y4gpu_pt_clear_film(y4gpu_ctx *ctx)
 	const size_t npx = (size_t) pt->h_scene.width * pt->h_scene.height;
 	Y4_CUDA(ctx, cudaMemsetAsync(pt->d_film_w, 0, npx * sizeof(float), ctx->stream));
 	Y4_CUDA(ctx, cudaMemsetAsync(pt->d_film_rgba, 0, npx * 4 * sizeof(float), ctx->stream));
+	return Y4GPU_OK;
+}
+
+int y4gpu_libm_eval(y4gpu_ctx *ctx, int fn, const float *a, const float *b, float *out, uint64_t n)
+{
+	if(!ctx || !a || !out || fn < 0 || fn > 3 || (fn == 3 && !b)) return Y4GPU_ERR_ARG;
+	if(!n) return Y4GPU_OK;
+	std::lock_guard<std::mutex> lock(ctx->mtx);
+	Y4_CUDA(ctx, cudaSetDevice(ctx->device));
+	float *d = nullptr;
+	Y4_CUDA(ctx, cudaMalloc((void **) &d, 3 * n * sizeof(float)));
+	cudaError_t e = cudaMemcpyAsync(d, a, n * sizeof(float), cudaMemcpyDefault, ctx->stream);
+	if(e == cudaSuccess && fn == 3) e = cudaMemcpyAsync(d + n, b, n * sizeof(float), cudaMemcpyDefault, ctx->stream);
+	if(e == cudaSuccess)
+	{
+		k_libm_eval<<<(unsigned) ((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8), 256, 0, ctx->stream>>>(fn, d, d + n, d + 2 * n, n);
+		e = cudaGetLastError();
+	}
+	if(e == cudaSuccess) e = cudaMemcpyAsync(out, d + 2 * n, n * sizeof(float), cudaMemcpyDefault, ctx->stream);
+	if(e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+	cudaFree(d);
+	if(e != cudaSuccess) { ctx->err = std::string("y4gpu_libm_eval: ") + cudaGetErrorString(e); return Y4GPU_ERR_CUDA; }
 	return Y4GPU_OK;
 }
 

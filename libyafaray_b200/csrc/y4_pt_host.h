@@ -31,6 +31,7 @@ inline Y4PtCamera derive_camera(const y4gpu_pt_camera &c)
 	Y4PtCamera o;
 	const HV position = hv(c.from), look = hv(c.to), up = hv(c.up);
 	const float aspect_ratio = c.aspect_ratio * (float) c.resy / (float) c.resx;
+	o.ang_aspect = aspect_ratio; o.ang_focal = 1.f; o.ang_max_radius = 0.f; o.ang_circular = c.circular; o.ang_projection = c.projection;
 	HV cam_y = up - position;
 	HV cam_z = look - position;
 	HV cam_x = cam_z ^ cam_y;
@@ -56,6 +57,20 @@ inline Y4PtCamera derive_camera(const y4gpu_pt_camera &c)
 		vup = vup * sy; vright = vright * sx;
 	}
 	else if(c.type == Y4GPU_CAM_EQUIRECTANGULAR) { vup = cam_y; vto = cam_z; }     // EquirectangularCamera::setAxis
+	else if(c.type == Y4GPU_CAM_ANGULAR)
+	{
+		// AngularCamera::factory + ctor + setAxis (camera_angular.cc:30-55,113-115): the angles are double parameters times the
+		// long double pi / 180, narrowed to the constructor's float arguments; std::tan(float) is this host's libm
+		const float angle = (float) ((long double) c.angle_degrees * 0.01745329251994329576923690768489L);
+		const float max_angle = (float) ((long double) c.max_angle_degrees * 0.01745329251994329576923690768489L);
+		vright = c.mirrored ? HV{-cam_x.x, -cam_x.y, -cam_x.z} : cam_x; vup = cam_y; vto = cam_z;
+		o.ang_max_radius = max_angle / angle;
+		if(c.projection == Y4GPU_ANGULAR_ORTHOGRAPHIC) o.ang_focal = 1.f / y4_fast_sin(angle);
+		else if(c.projection == Y4GPU_ANGULAR_STEREOGRAPHIC) o.ang_focal = 1.f / 2.f / tanf(angle / 2.f);
+		else if(c.projection == Y4GPU_ANGULAR_EQUISOLID_ANGLE) o.ang_focal = 1.f / 2.f / y4_fast_sin(angle / 2.f);
+		else if(c.projection == Y4GPU_ANGULAR_RECTILINEAR) o.ang_focal = 1.f / tanf(angle);
+		else o.ang_focal = 1.f / angle;
+	}
 	else
 	{
 		vup = {vup.x / (float) c.resy, vup.y / (float) c.resy, vup.z / (float) c.resy};

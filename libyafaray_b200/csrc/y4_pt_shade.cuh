@@ -16,6 +16,7 @@
 #pragma once
 #include "y4_pt_types.cuh"
 #include "y4_tri.cuh"
+#include "y4_libm.cuh"
 
 // ---- surface ---------------------------------------------------------------------------------
 // Per-triangle shading record, computed once per scene: the face normal of calculateNormal
@@ -449,14 +450,15 @@ Y4_HD float y4_bg_pdf(float p0, float p1, float s, bool inv)
 	if(inv) return fmaxf(0.000001f, xmul(xmul((float) Y4_2PI, y4_bg_sin_sample(s)), y4_bg_clamp_zero(xmul(p0, p1))));
 	return fmaxf(0.000001f, xmul(xmul(xmul(p0, p1), (float) Y4_1_2PI), y4_bg_clamp_zero(y4_bg_sin_sample(s))));
 }
-// Texture::invSphereMap / sphereMap (src/texture/texture.cc:103-132); acos is libm's on the host
+// Texture::invSphereMap / sphereMap (src/texture/texture.cc:103-132); std::acos / std::asin with the C library's bits (y4_libm.cuh)
 Y4_HD V3 y4_inv_sphere_map(float u, float v)
 {
 	const float theta = (float) xdmul((Y4_WIDE) v, Y4_PI), phi = -(float) xdmul((Y4_WIDE) u, Y4_2PI);
 	const float costheta = y4_fast_cos(theta), sintheta = y4_fast_sin(theta), cosphi = y4_fast_cos(phi), sinphi = y4_fast_sin(phi);
 	return v3(xmul(sintheta, cosphi), xmul(sintheta, sinphi), -costheta);
 }
-Y4_HD float y4_acos(float x) { return x <= -1.f ? (float) Y4_PI : (x >= 1.f ? 0.f : acosf(x)); }                     // math::acos
+Y4_HD float y4_acos(float x) { return x <= -1.f ? (float) Y4_PI : (x >= 1.f ? 0.f : y4_libm_acosf(x)); }            // math::acos (math.h:253-259)
+Y4_HD float y4_asin(float x) { return x <= -1.f ? (float) -Y4_PI_2 : (x >= 1.f ? (float) Y4_PI_2 : y4_libm_asinf(x)); }   // math::asin (math.h:261-267)
 Y4_HD void y4_sphere_map(const V3 p, float &u, float &v)
 {
 	const float sqrt_r_phi = xadd(xmul(p.x, p.x), xmul(p.y, p.y));

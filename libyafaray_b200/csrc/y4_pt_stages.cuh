@@ -160,9 +160,39 @@ Y4_HD void y4_lens_uv(const Y4PtCamera &cam, float r_1, float r_2, float &u, flo
 	else y4_shirley_disk(r_1, r_2, u, v);
 }
 
+// A camera that refuses a pixel position (CameraRay::valid_ == false: outside the circle of a circular angular camera) hands
+// back a ray with a zero direction and an empty interval: nothing can hit it, and the camera-hit stage turns it into the
+// sample renderTile adds for it, the layer's default colour (0, 0, 0, alpha 1: integrator_tiled.cc:343-347, layer_definitions.h:118).
+Y4_HD Y4Ray y4_invalid_camera_ray(const V3 from) { return y4_mk_ray(from, 1.f, v3(0.f, 0.f, 0.f), 0.f); }
+Y4_HD bool y4_camera_ray_invalid(const Y4Ray &r) { return r.dx == 0.f && r.dy == 0.f && r.dz == 0.f; }
+
+// AngularCamera::shootRay (camera_angular.cc:57-78).  std::atan2 / std::atan / std::asin are the C library's: y4_libm.cuh
+Y4_HD Y4Ray y4_angular_camera_ray(const Y4PtCamera &cam, float px, float py)
+{
+	const float u = xsub(1.f, xmul(2.f, xdiv(px, (float) cam.resx)));
+	float v = xsub(xmul(2.f, xdiv(py, (float) cam.resy)), 1.f);
+	v = xmul(v, cam.ang_aspect);
+	const float radius = xsqrt(xadd(xmul(u, u), xmul(v, v)));
+	if(cam.ang_circular && radius > cam.ang_max_radius) return y4_invalid_camera_ray(cam.pos);
+	float theta = 0.f;
+	if(!(u == 0.f && v == 0.f)) theta = y4_libm_atan2f(v, u);
+	float phi;
+	if(cam.ang_projection == Y4GPU_ANGULAR_ORTHOGRAPHIC) phi = y4_asin(xdiv(radius, cam.ang_focal));
+	else if(cam.ang_projection == Y4GPU_ANGULAR_STEREOGRAPHIC) phi = xmul(2.f, y4_libm_atanf(xdiv(radius, xmul(2.f, cam.ang_focal))));
+	else if(cam.ang_projection == Y4GPU_ANGULAR_EQUISOLID_ANGLE) phi = xmul(2.f, y4_asin(xdiv(radius, xmul(2.f, cam.ang_focal))));
+	else if(cam.ang_projection == Y4GPU_ANGULAR_RECTILINEAR) phi = y4_libm_atanf(xdiv(radius, cam.ang_focal));
+	else phi = xdiv(radius, cam.ang_focal);
+	const V3 in_plane = xadd3(xscale(cam.vright, y4_fast_cos(theta)), xscale(cam.vup, y4_fast_sin(theta)));
+	const V3 d = xadd3(xscale(in_plane, y4_fast_sin(phi)), xscale(cam.vto, y4_fast_cos(phi)));
+	const float tmin = xdiv(xdot(cam.near_n, xsub3(cam.near_p, cam.pos)), xdot(d, cam.near_n));
+	const float tmax = xdiv(xdot(cam.far_n, xsub3(cam.far_p, cam.pos)), xdot(d, cam.far_n));
+	return y4_mk_ray(cam.pos, tmin, d, tmax);
+}
+
 // PerspectiveCamera::shootRay (camera_perspective.cc:128-146); lu, lv: lens sample (used when aperture != 0)
 Y4_HD Y4Ray y4_camera_ray(const Y4PtCamera &cam, float px, float py, float lu, float lv)
 {
+	if(cam.type == Y4GPU_CAM_ANGULAR) return y4_angular_camera_ray(cam, px, py);
 	if(cam.type == Y4GPU_CAM_ORTHOGRAPHIC || cam.type == Y4GPU_CAM_EQUIRECTANGULAR)
 	{
 		// OrthographicCamera::shootRay (camera_orthographic.cc:52-60) / EquirectangularCamera::shootRay (camera_equirectangular.cc:50-62)
@@ -272,8 +302,9 @@ Y4_HD int y4_pt_primary(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, int 
 	const uint32_t spec = level > 0 ? (f & (uint32_t) (Y4_PF_SPEC | Y4_PF_ACC)) : 0u;      // f in: the flags the level above left
 	if(h.prim < 0)
 	{
-		const bool transp = sc.transp_background != 0 && (level == 0 || sc.transp_refracted_background != 0);   // TiledIntegrator::background
-		const C3 bg = transp ? c3f(0.f) : y4_background(sc, v3(r.dx, r.dy, r.dz));
+		const bool invalid = level == 0 && y4_camera_ray_invalid(r);         // no camera ray for this position: default colour
+		const bool transp = !invalid && sc.transp_background != 0 && (level == 0 || sc.transp_refracted_background != 0);   // TiledIntegrator::background
+		const C3 bg = (transp || invalid) ? c3f(0.f) : y4_background(sc, v3(r.dx, r.dy, r.dz));
 		st4(W.col, i, f4(bg.r, bg.g, bg.b, transp ? 0.f : 1.f));
 		f = spec;
 		return 0;
@@ -816,7 +847,8 @@ Y4_HD uint32_t y4_stage_primary3(const Y4PtScene &sc, const Y4PtWave &W, const Y
 	V3 dir[2]; C3 col[2];
 	if(h.prim < 0)
 	{
-		y4_tree_fold(W, i, f, y4_background(sc, v3(r.dx, r.dy, r.dz)));
+		const bool invalid = !(f & Y4_PF_SPEC) && y4_camera_ray_invalid(r);
+		y4_tree_fold(W, i, f, invalid ? c3f(0.f) : y4_background(sc, v3(r.dx, r.dy, r.dz)));
 		return y4_tree_next(sc, W, i, f, level, v3(0.f, 0.f, 0.f), 0, dir, col);
 	}
 	st_hit(W.hit0, i, h);

@@ -38,6 +38,9 @@ struct Y4PtCamera          // PerspectiveCamera state after ctor + setAxis (came
 	int type;                   // Y4GPU_CAM_*: perspective and architect share shootRay, they differ in vup / vto
 	int bkhtype, bkhbias;       // BokehType / BkhBiasType (camera_perspective.h:38-39)
 	float ls[16];               // polygon corner directions of the tri / square / penta / hexa lenses (ctor, :40-52)
+	// AngularCamera state (camera_angular.cc:30-44): aspect_ratio_, focal_length_, max_radius_, circular_, projection_
+	float ang_aspect, ang_focal, ang_max_radius;
+	int ang_circular, ang_projection;
 };
 
 struct Y4PtMaterial

@@ -263,7 +263,7 @@ class Interface:
 
     def createCamera(self, name):
         p = dict(self.params)
-        if p.get("type") not in _lib.CAMERA_TYPES:      # `angular` draws its ray from libm atan2 / tan: not restated
+        if p.get("type") not in _lib.CAMERA_TYPES:
             raise Y4Error(f"camera type '{p.get('type')}' is not supported by the GPU back end")
         self.cameras[name] = p
         return True
@@ -507,7 +507,12 @@ class Interface:
             cam.aperture, cam.dof_distance = float(cam_p.get("aperture", 0.0)), float(cam_p.get("dof_distance", 0.0))
         # the factories' own defaults (camera_equirectangular.cc:70: farClip -1e38)
         cam.near_clip = float(cam_p.get("nearClip", 0.0))
-        cam.far_clip = float(cam_p.get("farClip", -1.0e38 if cam.type == _lib.CAMERA_TYPES["equirectangular"] else -1.0))
+        cam.far_clip = float(cam_p.get("farClip", -1.0e38 if cam.type in (_lib.CAMERA_TYPES["equirectangular"], _lib.CAMERA_TYPES["angular"]) else -1.0))
+        if cam.type == _lib.CAMERA_TYPES["angular"]:      # AngularCamera::factory (camera_angular.cc:80-117); unknown projection names: equidistant
+            cam.angle_degrees = float(cam_p.get("angle", 90.0))
+            cam.max_angle_degrees = float(cam_p.get("max_angle", cam.angle_degrees))
+            cam.circular, cam.mirrored = int(bool(cam_p.get("circular", True))), int(bool(cam_p.get("mirrored", False)))
+            cam.projection = _lib.ANGULAR_PROJECTIONS.get(str(cam_p.get("projection", "")), 0)
         # unknown names select the defaults, like PerspectiveCamera::factory (camera_perspective.cc:207-218)
         cam.bokeh_type = _lib.BOKEH_TYPES.get(str(cam_p.get("bokeh_type", "disk1")), 0)
         cam.bokeh_bias = _lib.BOKEH_BIAS.get(str(cam_p.get("bokeh_bias", "uniform")), 0)

@@ -183,6 +183,34 @@ def make_portal():
     np.savez_compressed(os.path.join(HERE, "pt_portal.npz"), **out)
 
 
+# `angular` camera from inside the box: every projection, the circular mask (pixels without a camera ray: black, alpha 1),
+# mirrored, with a box filter and a gauss filter, and once through the specular ray tree -> pt_angular.npz
+_INSIDE = {"from": (0.5, 0.5, 0.25), "to": (0.52, 0.45, 1.0), "up": (0.5, 1.5, 0.25)}
+PT_GOLDEN_ANGULAR = {
+    "angular_equidistant_circular": dict(width=64, height=36, spp=3, bounces=3, camera_extra={"type": "angular", "angle": 90.0, **_INSIDE}),
+    "angular_stereographic_mirrored": dict(width=64, height=36, spp=3, bounces=2,
+                                           camera_extra={"type": "angular", "angle": 70.0, "circular": False, "mirrored": True, "projection": "stereographic", **_INSIDE}),
+    "angular_orthographic_max_angle": dict(width=64, height=48, spp=2, bounces=2,
+                                           camera_extra={"type": "angular", "angle": 80.0, "max_angle": 60.0, "projection": "orthographic", **_INSIDE}),
+    "angular_equisolid_gauss": dict(width=64, height=36, spp=3, bounces=3, filter_type="gauss",
+                                    camera_extra={"type": "angular", "angle": 100.0, "max_angle": 85.0, "projection": "equisolid_angle", **_INSIDE}),
+    "angular_rectilinear_glass": dict(width=64, height=36, spp=2, bounces=3, smooth_sphere=30.0, glass={"objects": ("sphere",), "IOR": 1.5},
+                                      camera_extra={"type": "angular", "angle": 50.0, "max_angle": 40.0, "projection": "rectilinear", **_INSIDE}),
+    "angular_direct_wide": dict(width=64, height=36, spp=2, bounces=2, integrator="directlighting", light_samples=2,
+                                camera_extra={"type": "angular", "angle": 120.0, "max_angle": 110.0, **_INSIDE}),
+}
+
+
+def make_angular():
+    out = {}
+    for key, kw in PT_GOLDEN_ANGULAR.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print(key, float(out[key][..., :3].mean()), float(out[key][..., 3].min()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_angular.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -213,6 +241,8 @@ if __name__ == "__main__":
         make_spot_soft()
     if "portal" in what:
         make_portal()
+    if "angular" in what:
+        make_angular()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

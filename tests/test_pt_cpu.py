@@ -170,7 +170,7 @@ def test_interface_rejects_unsupported_features():
     with pytest.raises(Y4Error):
         yi.createMaterial("t")
     yi.paramsClearAll()
-    yi.paramsSetString("type", "angular")
+    yi.paramsSetString("type", "fisheye")              # not a camera type of the reference (Camera::factory returns nullptr)
     with pytest.raises(Y4Error):
         yi.createCamera("c")
     yi.paramsClearAll()
@@ -452,6 +452,29 @@ def test_background_portal_light_vs_golden_reference_render(key):
     w, rgba = helpers.emu_pt_render(a)
     img = interface.normalize_film(w, rgba)
     assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
+ANGULAR_KEYS = ["angular_equidistant_circular", "angular_stereographic_mirrored", "angular_orthographic_max_angle", "angular_equisolid_gauss",
+                "angular_rectilinear_glass", "angular_direct_wide"]
+
+
+@pytest.mark.parametrize("key", ANGULAR_KEYS)
+def test_angular_camera_vs_golden_reference_render(key):
+    """AngularCamera::shootRay: the five projections (atan2 / atan / asin with the C library's bits, csrc/y4_libm.cuh), mirrored,
+    and the circular mask -- positions without a camera ray get the layer's default colour (black, alpha 1) with their full
+    filter footprint; once through the specular ray tree."""
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_ANGULAR
+    ref = np.load(os.path.join(GOLD, "pt_angular.npz"))[key]
+    a = _assemble(**PT_GOLDEN_ANGULAR[key])
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    if key != "angular_stereographic_mirrored":
+        assert (ref[0, 0] == (0.0, 0.0, 0.0, 1.0)).all() and (img[0, 0] == (0.0, 0.0, 0.0, 1.0)).all()
     p = helpers.psnr(img, ref)
     assert p >= PSNR_MIN, p
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
