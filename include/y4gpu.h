@@ -342,6 +342,13 @@ typedef struct y4gpu_pt_params
 	int32_t transp_refracted_background;   /* bg_transp_refract (TiledIntegrator::background, integrator_tiled.cc:707-720) */
 	int32_t background_gradient;  /* 0: `constant` background (colour in `background`); 1: `gradientback` (background_gradient.cc:34-46) */
 	float bg_gradient[4][3];      /* gradientback colours * power: zenith_ground, horizon_ground, zenith, horizon */
+	/* ambient occlusion of the direct-lighting integrator (do_AO, AO_samples, AO_distance, AO_color; integrator_direct_light.cc:124,
+	   TiledIntegrator::sampleAmbientOcclusion, integrator_tiled.cc:644-692): after the lights, every diffuse vertex integrate() reaches
+	   takes ao_samples BSDF-sampled occlusion rays of length ao_distance.  Used when path_samples == 0 only -- the reference's path
+	   tracer parses the parameters but never adds the term to the Combined layer.  ao_samples <= 0: off. */
+	int32_t ao_samples;
+	float ao_distance;
+	float ao_color[3];
 } y4gpu_pt_params;
 
 typedef struct y4gpu_pt_stats

@@ -136,7 +136,8 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 		// ---- integrator ------------------------------------------------------------------------------------------------------
 		const ParamMap &ip = params_;
 		const std::string itype = getStr(ip, "type");
-		if(get<bool>(ip, "caustics", false) || get<bool>(ip, "do_AO", false)) unsupported("photon caustics / ambient occlusion");
+		if(get<bool>(ip, "caustics", false)) unsupported("photon caustics");
+		if(get<bool>(ip, "do_AO", false) && get<int>(ip, "AO_samples", 32) < 1) unsupported("do_AO with AO_samples < 1");
 		const std::string caustic_type = getStr(ip, "caustic_type", "path");
 		if(caustic_type == "photon" || caustic_type == "both") unsupported("photon caustics");
 		y4gpu_pt_params pr;
@@ -150,6 +151,12 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 		pr.transp_refracted_background = get<bool>(ip, "bg_transp_refract", false);
 		pr.trace_caustics = itype == "pathtracing" && caustic_type != "none";
 		pr.transp_shadows = get<bool>(ip, "transpShad", false); pr.shadow_depth = get<int>(ip, "shadowDepth", 5);
+		if(get<bool>(ip, "do_AO", false) && itype == "directlighting")     // integrator_direct_light.cc:124,170-173 (the path tracer never adds AO to Combined)
+		{
+			pr.ao_samples = get<int>(ip, "AO_samples", 32);
+			pr.ao_distance = (float) get<double>(ip, "AO_distance", 1.0);
+			put3(pr.ao_color, getCol(ip, "AO_color", Rgb{1.f}));
+		}
 		// ---- camera ------------------------------------------------------------------------------------------------------------
 		const std::string view_name = render_view->getName();
 		const auto vp = rec.render_views.find(view_name);

@@ -97,7 +97,8 @@ class PtParams(C.Structure):
                 ("shadow_bias_auto", C.c_int32), ("shadow_bias", C.c_float), ("min_raydist_auto", C.c_int32), ("min_raydist", C.c_float),
                 ("base_sampling_offset", C.c_uint32), ("rr_seed", C.c_uint32), ("wave_size", C.c_uint32), ("profile", C.c_int32),
                 ("transp_shadows", C.c_int32), ("shadow_depth", C.c_int32), ("raydepth", C.c_int32), ("trace_caustics", C.c_int32),
-                ("transp_refracted_background", C.c_int32), ("background_gradient", C.c_int32), ("bg_gradient", (C.c_float * 3) * 4)]  # fmt: skip
+                ("transp_refracted_background", C.c_int32), ("background_gradient", C.c_int32), ("bg_gradient", (C.c_float * 3) * 4),
+                ("ao_samples", C.c_int32), ("ao_distance", C.c_float), ("ao_color", C.c_float * 3)]  # fmt: skip
 
 
 class PtStats(C.Structure):

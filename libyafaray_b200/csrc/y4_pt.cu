@@ -602,6 +602,9 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	sc.bg_gz = c3(params->bg_gradient[0][0], params->bg_gradient[0][1], params->bg_gradient[0][2]); sc.bg_gh = c3(params->bg_gradient[1][0], params->bg_gradient[1][1], params->bg_gradient[1][2]);
 	sc.bg_sz = c3(params->bg_gradient[2][0], params->bg_gradient[2][1], params->bg_gradient[2][2]); sc.bg_sh = c3(params->bg_gradient[3][0], params->bg_gradient[3][1], params->bg_gradient[3][2]);
 	sc.raydepth = params->raydepth; sc.trace_caustics = params->trace_caustics; sc.transp_refracted_background = params->transp_refracted_background;
+	// ambient occlusion belongs to DirectLightIntegrator::integrate only (the path tracer never adds it to the Combined layer)
+	sc.ao_samples = (params->path_samples == 0 && params->ao_samples > 0) ? params->ao_samples : 0;
+	sc.ao_dist = params->ao_distance; sc.ao_col = c3(params->ao_color[0], params->ao_color[1], params->ao_color[2]);
 	sc.has_specular = 0;
 	for(uint32_t m = 0; m < n_mat; ++m)
 	{
@@ -1010,6 +1013,7 @@ extern "C" int y4gpu_pt_render_pass(y4gpu_ctx *ctx, int n_samples, int offset, i
 	std::vector<std::pair<int, int>> all_lk;
 	for(int l = 0; l < sc.n_lights; ++l)
 		for(int k = 0, ns = y4_light_num_samples(sc, pt->h_lights[l]); k < ns; ++k) all_lk.push_back(std::make_pair(l, k));
+	for(int k = 0; k < sc.ao_samples; ++k) all_lk.push_back(std::make_pair(sc.n_lights, k));     // then sampleAmbientOcclusion: pseudo-light n_lights
 	const int max_ls = pt->max_light_samples;
 	// counter slots: [0..5] traversal visit counters (profile mode), then one per queue / trace launch
 	const uint64_t n_waves = total ? (total + wave_size - 1) / wave_size : 0;

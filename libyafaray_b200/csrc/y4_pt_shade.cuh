@@ -725,6 +725,27 @@ Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, f
 	return true;
 }
 
+// One sample of TiledIntegrator::sampleAmbientOcclusion (integrator_tiled.cc:654-690, clay == false): a BSDF-sampled direction
+// (Glossy | Diffuse | Reflect), an occlusion ray of length ao_dist; unoccluded it adds ao_col * surf_col * |n . dir| * w.
+// Slot 1 carries "col += sp.emit(wo) * s.pdf_", which needs no ray.
+Y4_HD void y4_ao_sample(const Y4PtScene &sc, const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo, float s1, float s2, Y4DirectOut &out)
+{
+	out.valid[0] = out.valid[1] = false;
+	out.contrib[0] = out.contrib[1] = c3f(0.f);
+	out.ray[0] = out.ray[1] = y4_null_ray();
+	const float tmin_shadow = sc.shadow_bias_auto ? xmul(sc.shadow_bias, fmaxf(1.f, xlen(sp.p))) : sc.shadow_bias;
+	V3 wi = v3(0.f, 0.f, 0.f);
+	float w = 0.f, pdf = 0.f; bool sampled, specular;
+	const uint32_t fl = Y4_BSDF_GLOSSY | Y4_BSDF_DIFFUSE | Y4_BSDF_REFLECT;
+	const C3 surf = y4_mat_sample(m, sp, wo, s1, s2, fl, wi, w, pdf, sampled, specular);
+	if(m.bsdf_flags & Y4_BSDF_EMIT) out.contrib[1] = cscale(y4_mat_emit(m, sp, wo), pdf);
+	if(!sampled) return;                                   // direction left at zero: |n . dir| = 0, nothing to add
+	const float cosv = fabsf(xdot(sp.n, wi));
+	out.contrib[0] = cscale(cscale(cmul(sc.ao_col, surf), cosv), w);
+	out.ray[0] = y4_mk_ray(sp.p, tmin_shadow, wi, sc.ao_dist);
+	out.valid[0] = true;
+}
+
 template<bool GENERAL = true>
 Y4_HD void y4_direct_sample(const Y4PtScene &sc, const Y4PtLight &L, const Y4PtMaterial &m, const Y4Surf &sp, const V3 wo,
                             float s1, float s2, Y4DirectOut &out)

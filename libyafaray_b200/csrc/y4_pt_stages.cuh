@@ -356,7 +356,8 @@ Y4_HD bool y4_direct_active(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, 
 {
 	if(!(f & Y4_PF_DIRECT)) return false;          // set by the camera-hit / path-vertex step, cleared when the estimate is folded in
 	l = all_lights ? light : (sc.n_lights > 1 ? (int) W.lnum[i] : 0);
-	num_samples = y4_light_num_samples(sc, sc.lights[l]);
+	// l == n_lights: the ambient-occlusion samples (camera-hit estimates only: the test folds away in the path-vertex kernels)
+	num_samples = (all_lights && l == sc.n_lights) ? sc.ao_samples : y4_light_num_samples(sc, sc.lights[l]);
 	return k < num_samples;
 }
 
@@ -364,11 +365,13 @@ Y4_HD bool y4_direct_active(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, 
 // (integrator_montecarlo.cc:398-404: Halton(2) and Halton(3) started at num_samples * sample + offset + l * 4567 - 1,
 // advanced k + 1 times).  They depend on the pixel-sample, the light and k only -- not on the vertex -- so the last
 // pair is kept in W.lsamp and reused down the path.
-Y4_HD void y4_light_sample_numbers(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l, int k, int num_samples, float4 cache, float &s1, float &s2)
+Y4_HD void y4_light_sample_numbers(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &ps, uint32_t i, int l, int k, int num_samples, float4 cache, float &s1, float &s2,
+                                   bool ao = false)
 {
 	if(y4_f2u(cache.z) == (uint32_t) l && y4_f2u(cache.w) == (uint32_t) k) { s1 = cache.x; s2 = cache.y; return; }
 	const Y4PixelId s = y4_pixel_id(sc, ps, W.pix[i], W.samp[i]);
-	const uint32_t offs = (uint32_t) num_samples * s.sample + s.offset + (uint32_t) l * 4567u;
+	// sampleAmbientOcclusion starts its two sequences at n * sample + offset - 1 (integrator_tiled.cc:651-653): no per-light term
+	const uint32_t offs = (uint32_t) num_samples * s.sample + s.offset + (ao ? 0u : (uint32_t) l * 4567u);
 	s1 = y4_halton2_at(offs - 1u, (uint32_t) k + 1u);
 	Y4Halton h3 = y4_halton_start(3u, offs - 1u);
 	for(int q = 0; q <= k; ++q) s2 = y4_halton_next(h3);
@@ -386,12 +389,14 @@ Y4_HD uint32_t y4_pt_direct(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPa
 	f &= ~(uint32_t) (Y4_PF_S0 | Y4_PF_S1 | Y4_PF_C1);
 	int l, num_samples;
 	if(!y4_direct_active(sc, W, i, f, all_lights, light, k, l, num_samples)) return 0u;
-	const Y4PtLight &L = sc.lights[l];
+	const bool ao = all_lights && l == sc.n_lights;
+	const Y4PtLight &L = sc.lights[ao ? 0 : l];
 	float s1 = 0.f, s2 = 0.f;
-	if(!y4_light_dirac(L.type)) y4_light_sample_numbers(sc, W, ps, i, l, k, num_samples, cache, s1, s2);
+	if(ao || !y4_light_dirac(L.type)) y4_light_sample_numbers(sc, W, ps, i, l, k, num_samples, cache, s1, s2, ao);
 	Y4DirectOut out;
-	y4_direct_sample<SPEC>(sc, L, vx.m, vx.sp, vx.wo, s1, s2, out);
-	const bool cast = L.cast_shadows && vx.m.receive_shadows;
+	if(ao) y4_ao_sample(sc, vx.m, vx.sp, vx.wo, s1, s2, out);
+	else y4_direct_sample<SPEC>(sc, L, vx.m, vx.sp, vx.wo, s1, s2, out);
+	const bool cast = ao || (L.cast_shadows && vx.m.receive_shadows);      // occlusion rays are traced whatever receive_shadows says
 	uint32_t mask = 0u;
 	for(int q = 0; q < 2; ++q)
 	{
@@ -433,7 +438,8 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 	const float4 base = all_lights ? ld4(W.col, i) : ld4(W.pcol, i);
 	const float4 thr4 = all_lights ? zero4 : ld4(W.pthr, i);
 	const float4 lc4 = (all_lights || !(f & Y4_PF_LCOL)) ? zero4 : ld4(W.lcol, i);
-	const Y4PtLight &L = sc.lights[l];
+	const bool ao = all_lights && l == sc.n_lights;
+	const Y4PtLight &L = sc.lights[ao ? 0 : l];
 	// running sums over the light's samples live in acc_a/acc_b only between samples (k > 0)
 	C3 a = c3f(0.f), b = c3f(0.f);
 	if(k > 0) { a = ld3(W.acc_a, i); b = ld3(W.acc_b, i); }
@@ -443,7 +449,15 @@ Y4_HD void y4_pt_direct_resolve(const Y4PtScene &sc, const Y4PtWave &W, uint32_t
 	if(k < num_samples - 1) { st3(W.acc_a, i, a); st3(W.acc_b, i, b); return; }
 	// last sample of this light: doLightEstimation's result
 	C3 dl = c3f(0.f);
-	if(y4_light_dirac(L.type)) dl = cadd(dl, a);
+	if(ao)
+	{
+		// sampleAmbientOcclusion returns col / n (a division, integrator_tiled.cc:691); b holds the emission terms of an emitting
+		// diffuse material, which the reference adds between the occlusion terms (<= 1 ulp apart in that case, exact otherwise)
+		const float nf = (float) num_samples;
+		const C3 sum = cadd(a, b);                         // b == 0 unless the material emits: a + 0 is a
+		dl = c3(xdiv(sum.r, nf), xdiv(sum.g, nf), xdiv(sum.b, nf));
+	}
+	else if(y4_light_dirac(L.type)) dl = cadd(dl, a);
 	else
 	{
 		const float inv = xdiv(1.f, (float) num_samples);

@@ -134,6 +134,7 @@ struct Y4PtScene
 	uint32_t base_sampling_offset, rr_seed;
 	float aa_light_sample_multiplier;
 	int aa_passes;
+	int ao_samples; float ao_dist; C3 ao_col;     // ambient occlusion of the direct-lighting integrator (0 samples: off); sampled as pseudo-light n_lights
 	// film
 	int width, height, cx0, cy0;
 	double filterw, table_scale;

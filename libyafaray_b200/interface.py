@@ -290,8 +290,8 @@ class Interface:
             raise Y4Error("photon caustics are not supported by the GPU back end")
         if p.get("caustic_type", "path") in ("photon", "both"):
             raise Y4Error("photon caustics are not supported by the GPU back end")
-        if p.get("do_AO", False):
-            raise Y4Error("ambient occlusion in the path tracer is not supported by the GPU back end")
+        if p.get("do_AO", False) and int(p.get("AO_samples", 32)) < 1:
+            raise Y4Error("do_AO with AO_samples < 1 (the reference divides by zero) is not supported by the GPU back end")
         self.integrators[name] = p
         return True
 
@@ -661,6 +661,11 @@ class Interface:
         pr.raydepth, pr.transp_refracted_background = int(integ.get("raydepth", 5)), int(integ.get("bg_transp_refract", False))
         pr.trace_caustics = int(integ.get("type") == "pathtracing" and integ.get("caustic_type", "path") not in ("none", "photon"))
         pr.transp_shadows, pr.shadow_depth = int(bool(integ.get("transpShad", False))), int(integ.get("shadowDepth", 5))
+        # do_AO: DirectLightIntegrator adds sampleAmbientOcclusion at every diffuse vertex (integrator_direct_light.cc:124); the path
+        # tracer reads the same parameters but only feeds the AO layers with them (integrator_path_tracer.cc:277), never Combined
+        if integ.get("do_AO", False) and integ.get("type") == "directlighting":
+            pr.ao_samples, pr.ao_distance = int(integ.get("AO_samples", 32)), float(integ.get("AO_distance", 1.0))
+            pr.ao_color[:] = [float(x) for x in integ.get("AO_color", (1.0, 1.0, 1.0))[:3]]
         if bg is not None:
             c, pw = bg.get("color", (0.0, 0.0, 0.0, 1.0)), np.float32(bg.get("power", 1.0))
             pr.background[:] = [float(np.float32(c[k]) * pw) for k in range(3)]

@@ -120,6 +120,9 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	sc.bg_gz = c3(params->bg_gradient[0][0], params->bg_gradient[0][1], params->bg_gradient[0][2]); sc.bg_gh = c3(params->bg_gradient[1][0], params->bg_gradient[1][1], params->bg_gradient[1][2]);
 	sc.bg_sz = c3(params->bg_gradient[2][0], params->bg_gradient[2][1], params->bg_gradient[2][2]); sc.bg_sh = c3(params->bg_gradient[3][0], params->bg_gradient[3][1], params->bg_gradient[3][2]);
 	sc.raydepth = params->raydepth; sc.trace_caustics = params->trace_caustics; sc.transp_refracted_background = params->transp_refracted_background;
+	// ambient occlusion belongs to DirectLightIntegrator::integrate only (the path tracer never adds it to the Combined layer)
+	sc.ao_samples = (params->path_samples == 0 && params->ao_samples > 0) ? params->ao_samples : 0;
+	sc.ao_dist = params->ao_distance; sc.ao_col = c3(params->ao_color[0], params->ao_color[1], params->ao_color[2]);
 	sc.has_specular = 0;
 	for(uint32_t m = 0; m < n_mat; ++m)
 	{
@@ -209,6 +212,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	std::vector<std::pair<int, int>> all_lk;
 	for(int l = 0; l < sc.n_lights; ++l)
 		for(int k = 0; k < y4_light_num_samples(sc, hl[l]); ++k) all_lk.push_back(std::make_pair(l, k));
+	for(int k = 0; k < sc.ao_samples; ++k) all_lk.push_back(std::make_pair(sc.n_lights, k));
 	std::vector<uint32_t> q_hit0, q_shadow, q_cur, q_next;
 	const int l0 = all_lk.empty() ? -1 : all_lk[0].first;
 	std::vector<uint32_t> q_spec, q_spec_next;

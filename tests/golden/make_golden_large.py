@@ -211,6 +211,33 @@ def make_angular():
     np.savez_compressed(os.path.join(HERE, "pt_angular.npz"), **out)
 
 
+# do_AO on the direct-lighting integrator: TiledIntegrator::sampleAmbientOcclusion after the lights, at every diffuse vertex
+# integrate() reaches (also behind mirrors / glass) -> pt_ao.npz
+PT_GOLDEN_AO = {
+    "ao_default_color": dict(width=80, height=45, spp=2, bounces=2, integrator="directlighting", light_samples=2,
+                             integrator_extra={"do_AO": True, "AO_samples": 4, "AO_distance": 0.4}),
+    "ao_tinted_no_lamp_gauss": dict(width=80, height=45, spp=3, bounces=2, integrator="directlighting", lamp=False, filter_type="gauss", smooth_sphere=30.0,
+                                    integrator_extra={"do_AO": True, "AO_samples": 3, "AO_distance": 0.25, "AO_color": (0.9, 0.8, 0.6, 1.0)}),
+    "ao_behind_mirror_and_glass": dict(width=80, height=45, spp=2, bounces=2, integrator="directlighting", light_samples=1, smooth_sphere=30.0, box_lift=0.013,
+                                       glass={"objects": ("sphere",), "IOR": 1.5}, mirror={"objects": ("back",), "color": (0.9, 0.9, 0.9)},
+                                       integrator_extra={"do_AO": True, "AO_samples": 2, "AO_distance": 0.5, "raydepth": 3}),
+    "ao_transparent_shadows_glow": dict(width=80, height=45, spp=2, bounces=2, integrator="directlighting", light_samples=1, glow=0.3,
+                                        pane={"transparency": 0.7, "transmit_filter": 0.9},
+                                        integrator_extra={"do_AO": True, "AO_samples": 3, "AO_distance": 0.6, "transpShad": True, "shadowDepth": 4}),
+    "ao_ignored_by_the_path_tracer": dict(width=64, height=36, spp=2, bounces=3, integrator_extra={"do_AO": True, "AO_samples": 4, "AO_distance": 0.4}),
+}
+
+
+def make_ao():
+    out = {}
+    for key, kw in PT_GOLDEN_AO.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print(key, float(out[key][..., :3].mean()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_ao.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -243,6 +270,8 @@ if __name__ == "__main__":
         make_portal()
     if "angular" in what:
         make_angular()
+    if "ao" in what:
+        make_ao()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

@@ -480,6 +480,28 @@ def test_angular_camera_vs_golden_reference_render(key):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+AO_KEYS = ["ao_default_color", "ao_tinted_no_lamp_gauss", "ao_behind_mirror_and_glass", "ao_transparent_shadows_glow", "ao_ignored_by_the_path_tracer"]
+
+
+@pytest.mark.parametrize("key", AO_KEYS)
+def test_ambient_occlusion_of_direct_lighting_vs_golden_reference_render(key):
+    """do_AO: TiledIntegrator::sampleAmbientOcclusion after estimateAllDirectLight at every diffuse vertex integrate() reaches --
+    AO_samples BSDF-sampled occlusion rays of length AO_distance from Halton(2) / Halton(3), summed and divided by n; with
+    transparent shadows the blockers' filter colours; an emitting diffuse wall adds emit * pdf per sample.  The path tracer
+    parses the parameters and ignores them for the Combined layer (last key)."""
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_AO
+    ref = np.load(os.path.join(GOLD, "pt_ao.npz"))[key]
+    a = _assemble(**PT_GOLDEN_AO[key])
+    assert (a["params"].ao_samples > 0) == (key != "ao_ignored_by_the_path_tracer")
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 def _shiny2_cfgs():
     sys.path.insert(0, GOLD)
     from make_golden_large import PT_GOLDEN_SHINY2
