@@ -340,7 +340,8 @@ typedef struct y4gpu_pt_params
 	int32_t trace_caustics;       /* caustic_type path / both: emission found after a specular bounce of a path counts
 	                                 (integrator_path_tracer.cc:227,256-264) */
 	int32_t transp_refracted_background;   /* bg_transp_refract (TiledIntegrator::background, integrator_tiled.cc:707-720) */
-	int32_t background_gradient;  /* 0: `constant` background (colour in `background`); 1: `gradientback` (background_gradient.cc:34-46) */
+	int32_t background_gradient;  /* 0: `constant` background (colour in `background`); 1: `gradientback` (background_gradient.cc:34-46);
+	                                 2: `textureback` (background_texture.cc), described by the bg_texture* fields below */
 	float bg_gradient[4][3];      /* gradientback colours * power: zenith_ground, horizon_ground, zenith, horizon */
 	/* ambient occlusion of the direct-lighting integrator (do_AO, AO_samples, AO_distance, AO_color; integrator_direct_light.cc:124,
 	   TiledIntegrator::sampleAmbientOcclusion, integrator_tiled.cc:644-692): after the lights, every diffuse vertex integrate() reaches
@@ -349,6 +350,13 @@ typedef struct y4gpu_pt_params
 	int32_t ao_samples;
 	float ao_distance;
 	float ao_color[3];
+	/* textureback (TextureBackground::factory, background_texture.cc:80-151): an image texture seen in every direction */
+	int32_t bg_texture;           /* index into the array given to y4gpu_pt_set_textures (which therefore comes first) */
+	int32_t bg_texture_angular;   /* mapping "probe" / "angular": Texture::angMap; otherwise spherical (Texture::sphereMap) */
+	float bg_texture_rotation;    /* `rotation`, degrees */
+	float bg_texture_power;       /* `power` */
+	float bg_ibl_clamp;           /* `ibl_clamp_sampling`: BackgroundLight::intersect clamps the colour proportionally (0: off).
+	                                 `smartibl_blur` (mip-mapped lookups for the light) is not supported: callers refuse it */
 } y4gpu_pt_params;
 
 typedef struct y4gpu_pt_stats

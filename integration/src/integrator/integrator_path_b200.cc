@@ -283,6 +283,15 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 			else unsupported("material type '" + type + "'");
 		}
 		if(pr.transp_shadows && any_transparent_textured) unsupported("textured transparent materials with transpShad");
+		// a textureback's image travels with the material textures
+		const ParamMap *background_params = nullptr;
+		if(background_) for(const auto &kv : rec.backgrounds) if(scene.getBackground(kv.first) == background_) background_params = &kv.second;
+		if(background_params && getStr(*background_params, "type") == "textureback")
+		{
+			const std::string tname = getStr(*background_params, "texture");
+			if(!rec.textures.count(tname)) unsupported("textureback without a recorded texture");
+			if(!tex_index.count(tname)) { tex_index[tname] = (int) tex_names.size(); tex_names.push_back(tname); }
+		}
 		// ---- textures: the texels exactly as Image::getColor(x, y) returns them ----------------------------------------------------
 		std::vector<y4gpu_pt_texture> textures(tex_names.size());
 		std::vector<std::vector<float>> texels(tex_names.size());
@@ -417,13 +426,23 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 		std::string ibl_light_name;
 		if(background_)
 		{
-			const ParamMap *bp = nullptr;
-			for(const auto &kv : rec.backgrounds) if(scene.getBackground(kv.first) == background_) bp = &kv.second;
+			const ParamMap *bp = background_params;
 			if(!bp) unsupported("background without recorded parameters");
 			const std::string btype = getStr(*bp, "type");
-			if(btype != "constant" && btype != "gradientback") unsupported("backgrounds other than constant / gradientback");
+			if(btype != "constant" && btype != "gradientback" && btype != "textureback") unsupported("backgrounds other than constant / gradientback / textureback");
 			rendered_background_has_ibl = get<bool>(*bp, "ibl", false);
-			ibl_light_name = btype == "constant" ? "constantBackground_bgLight" : "GradientBackground_bgLight";
+			ibl_light_name = btype == "constant" ? "constantBackground_bgLight" : (btype == "gradientback" ? "GradientBackground_bgLight" : "textureBackground_bgLight");
+			if(btype == "textureback")       // TextureBackground::factory (background_texture.cc:80-151)
+			{
+				if(get<float>(*bp, "smartibl_blur", 0.f) > 0.f) unsupported("textureback with smartibl_blur");
+				const std::string mapping = getStr(*bp, "mapping");
+				pr.background_gradient = 2;
+				pr.bg_texture = tex_index.at(getStr(*bp, "texture"));
+				pr.bg_texture_angular = (mapping == "probe" || mapping == "angular") ? 1 : 0;
+				pr.bg_texture_rotation = get<float>(*bp, "rotation", 0.f);
+				pr.bg_texture_power = get<float>(*bp, "power", 1.f);
+				pr.bg_ibl_clamp = rendered_background_has_ibl ? get<float>(*bp, "ibl_clamp_sampling", 0.f) : 0.f;
+			}
 			const float pw = get<float>(*bp, "power", 1.f);
 			const Rgb c = getCol(*bp, "color", Rgb{0.f});
 			pr.background[0] = c.r_ * pw; pr.background[1] = c.g_ * pw; pr.background[2] = c.b_ * pw;

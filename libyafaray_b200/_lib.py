@@ -98,7 +98,9 @@ class PtParams(C.Structure):
                 ("base_sampling_offset", C.c_uint32), ("rr_seed", C.c_uint32), ("wave_size", C.c_uint32), ("profile", C.c_int32),
                 ("transp_shadows", C.c_int32), ("shadow_depth", C.c_int32), ("raydepth", C.c_int32), ("trace_caustics", C.c_int32),
                 ("transp_refracted_background", C.c_int32), ("background_gradient", C.c_int32), ("bg_gradient", (C.c_float * 3) * 4),
-                ("ao_samples", C.c_int32), ("ao_distance", C.c_float), ("ao_color", C.c_float * 3)]  # fmt: skip
+                ("ao_samples", C.c_int32), ("ao_distance", C.c_float), ("ao_color", C.c_float * 3),
+                ("bg_texture", C.c_int32), ("bg_texture_angular", C.c_int32), ("bg_texture_rotation", C.c_float), ("bg_texture_power", C.c_float),
+                ("bg_ibl_clamp", C.c_float)]  # fmt: skip
 
 
 class PtStats(C.Structure):

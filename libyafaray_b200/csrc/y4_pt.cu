@@ -24,6 +24,7 @@ struct Y4Pt
 	std::vector<float4 *> d_texels;
 	Y4PtTexture *d_textures = nullptr; Y4PtLayer *d_layers = nullptr; float *d_tri_orco = nullptr, *d_tri_uv = nullptr;
 	uint32_t n_textures = 0, n_layers = 0;
+	std::vector<Y4PtTexture> h_textures;        // the descriptors as uploaded (texels = device pointers): a textureback looks its image up here
 	uint8_t *d_sigma = nullptr; uint16_t *d_offset = nullptr, *d_prime = nullptr; double *d_inv_prime = nullptr, *d_sigma_d = nullptr; unsigned long long *d_magic = nullptr;
 	bool scene_set = false;
 	y4gpu_pt_params params = {};
@@ -75,6 +76,7 @@ static void pt_free_textures(Y4Pt *pt)
 	cudaFree(pt->d_textures); cudaFree(pt->d_layers); cudaFree(pt->d_tri_orco); cudaFree(pt->d_tri_uv);
 	pt->d_textures = nullptr; pt->d_layers = nullptr; pt->d_tri_orco = nullptr; pt->d_tri_uv = nullptr;
 	pt->n_textures = pt->n_layers = 0;
+	pt->h_textures.clear();
 }
 
 // ---- kernels -------------------------------------------------------------------------------------------
@@ -560,6 +562,7 @@ int y4gpu_pt_set_textures(y4gpu_ctx *ctx, const y4gpu_pt_texture *textures, uint
 	}
 	Y4_CUDA(ctx, cudaStreamSynchronize(st));            // the host vectors above go out of scope
 	pt->n_textures = n_tex; pt->n_layers = n_layers;
+	pt->h_textures = ht;
 	return Y4GPU_OK;
 }
 
@@ -635,6 +638,27 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	// object lights need the general kernel variant as well (not the ray levels)
 	for(uint32_t l = 0; l < n_light; ++l) if((lights[l].type == Y4GPU_LIGHT_OBJECT || lights[l].type == Y4GPU_LIGHT_BACKGROUND || lights[l].type == Y4GPU_LIGHT_SPOT_SOFT || lights[l].type == Y4GPU_LIGHT_PORTAL) && !sc.has_specular) sc.has_specular = 1;
 	sc.background = c3(params->background[0], params->background[1], params->background[2]);
+	// textureback: the image is one of the uploaded textures; lights that evaluate the background on the host (the IBL tables)
+	// get a host copy of its texels for the duration of this call
+	std::vector<float4> bg_texels_host;
+	Y4PtTexture bg_tex_host;
+	memset(&bg_tex_host, 0, sizeof(bg_tex_host));
+	if(params->background_gradient == 2)
+	{
+		if(params->bg_texture < 0 || (uint32_t) params->bg_texture >= pt->n_textures) { ctx->err = "textureback: bg_texture is not an uploaded texture (y4gpu_pt_set_textures comes first)"; return Y4GPU_ERR_ARG; }
+		sc.bg_tex = derive_texture_background(*params, pt->d_textures + params->bg_texture);
+		bool on_host = false;
+		for(uint32_t l = 0; l < n_light; ++l) on_host = on_host || lights[l].type == Y4GPU_LIGHT_BACKGROUND;
+		if(on_host)
+		{
+			bg_tex_host = pt->h_textures[params->bg_texture];
+			bg_texels_host.resize((size_t) bg_tex_host.w * bg_tex_host.h);
+			Y4_CUDA(ctx, cudaMemcpyAsync(bg_texels_host.data(), bg_tex_host.texels, bg_texels_host.size() * sizeof(float4), cudaMemcpyDeviceToHost, st));
+			Y4_CUDA(ctx, cudaStreamSynchronize(st));
+			bg_tex_host.texels = bg_texels_host.data();
+		}
+	}
+	else if(params->background_gradient < 0 || params->background_gradient > 2) { ctx->err = "unknown background type"; return Y4GPU_ERR_ARG; }
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
 	sc.base_sampling_offset = params->base_sampling_offset; sc.rr_seed = params->rr_seed;
@@ -651,7 +675,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	for(uint32_t i = 0; i < n_light; ++i)
 	{
 		pt->h_lights[i] = derive_light(lights[i]);
-		if(lights[i].type == Y4GPU_LIGHT_PORTAL) derive_light_background(pt->h_lights[i], *params);
+		if(lights[i].type == Y4GPU_LIGHT_PORTAL) derive_light_background(pt->h_lights[i], *params, pt->d_textures + (params->background_gradient == 2 ? params->bg_texture : 0));
 		if(lights[i].type == Y4GPU_LIGHT_OBJECT || lights[i].type == Y4GPU_LIGHT_PORTAL)
 		{
 			// the light's own copy of its mesh: vertices, geometric normals, area cdf (ObjectLight::initIs) in one device block
@@ -674,7 +698,8 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		{
 			// the tabulated background (BackgroundLight::init) in one device block: row offsets, function values, cdfs, 1 / integrals
 			std::vector<int> off; std::vector<float> func, cdf, inv_int;
-			derive_background_light(pt->h_lights[i], lights[i], *params, off, func, cdf, inv_int);
+			derive_background_light(pt->h_lights[i], lights[i], *params, off, func, cdf, inv_int, &bg_tex_host);
+			if(params->background_gradient == 2) pt->h_lights[i].bg_tex.tex = pt->d_textures + params->bg_texture;      // from here on: the device copy
 			const size_t b_off = off.size() * 4, b_f = func.size() * 4, b_i = inv_int.size() * 4;
 			char *blob = nullptr;
 			Y4_CUDA(ctx, cudaMalloc(&blob, b_off + 2 * b_f + b_i));

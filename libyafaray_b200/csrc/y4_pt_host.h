@@ -320,9 +320,22 @@ inline float derive_pdf1d(const float *func, int n, std::vector<float> &cdf)
 	return integral;
 }
 
-// the background a background / portal light evaluates (Background::eval): a copy of the render parameters' description
-inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p)
+// TextureBackground ctor (background_texture.cc:30-42): rotation_ = 2 rot / 360, its FAST_TRIG sine / cosine (long double pi)
+inline Y4BgTex derive_texture_background(const y4gpu_pt_params &p, const Y4PtTexture *tex)
 {
+	Y4BgTex b;
+	b.tex = tex; b.angular = p.bg_texture_angular; b.power = p.bg_texture_power;
+	b.rotation = 2.f * p.bg_texture_rotation / 360.f;
+	b.sin_r = y4_fast_sin((float) (3.1415926535897932384626433832795L * (long double) b.rotation));
+	b.cos_r = y4_fast_cos((float) (3.1415926535897932384626433832795L * (long double) b.rotation));
+	return b;
+}
+
+// the background a background / portal light evaluates (Background::eval): a copy of the render parameters' description
+// (tex: where the light finds the textureback's image -- a host copy while the IBL tables are derived, the device array after)
+inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p, const Y4PtTexture *tex = nullptr)
+{
+	if(p.background_gradient == 2) { o.bg_tex = derive_texture_background(p, tex); o.bg_clamp = p.bg_ibl_clamp; }
 	o.bg_gradient = p.background_gradient;
 	o.bg_col = c3(p.background[0], p.background[1], p.background[2]);
 	o.bg_gz = c3(p.bg_gradient[0][0], p.bg_gradient[0][1], p.bg_gradient[0][2]); o.bg_gh = c3(p.bg_gradient[1][0], p.bg_gradient[1][1], p.bg_gradient[1][2]);
@@ -333,10 +346,11 @@ inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p)
 // 16 + (int)(sin(theta) * 704) columns, a Pdf1D per row and one over the row integrals.  The caller stores the arrays
 // where the light's pointers can reach them; the background's own description is copied into the light for eval().
 inline void derive_background_light(Y4PtLight &o, const y4gpu_pt_light &l, const y4gpu_pt_params &p,
-                                    std::vector<int> &off, std::vector<float> &func, std::vector<float> &cdf, std::vector<float> &inv_int)
+                                    std::vector<int> &off, std::vector<float> &func, std::vector<float> &cdf, std::vector<float> &inv_int,
+                                    const Y4PtTexture *host_tex = nullptr)
 {
 	o.bg_abs_inter = l.double_sided;
-	derive_light_background(o, p);
+	derive_light_background(o, p, host_tex);
 	const int nv = 360, max_u = 720, min_u = 16;
 	o.bg_nv = nv;
 	off.clear(); func.clear(); cdf.clear(); inv_int.clear();

@@ -17,6 +17,7 @@
 #include "y4_pt_types.cuh"
 #include "y4_tri.cuh"
 #include "y4_libm.cuh"
+#include "y4_pt_tex.cuh"
 
 // ---- surface ---------------------------------------------------------------------------------
 // Per-triangle shading record, computed once per scene: the face normal of calculateNormal
@@ -416,8 +417,10 @@ Y4_HD bool y4_light_illuminate(const Y4PtLight &L, const V3 p, Y4LSample &ls)
 
 // ---- background light (src/light/light_background.cc) ------------------------------------------------------------
 // ConstantBackground::eval / GradientBackground::eval (background_gradient.cc:34-46)
+Y4_HD C3 y4_texture_background(const Y4BgTex &B, const V3 dir);
 Y4_HD C3 y4_bg_eval(const Y4PtLight &L, const V3 dir)
 {
+	if(L.bg_gradient == 2) return y4_texture_background(L.bg_tex, dir);
 	if(!L.bg_gradient) return L.bg_col;
 	float blend = dir.z;
 	C3 color;
@@ -471,6 +474,58 @@ Y4_HD void y4_sphere_map(const V3 p, float &u, float &v)
 		u = xsub(1.f, phi_ratio);
 	}
 	v = (float) (1.0 - xdmul((Y4_WIDE) y4_acos(xdiv(p.z, xsqrt(sqrt_r_theta))), Y4_1_PI));
+}
+// Texture::angMap (texture.cc:75-86)
+Y4_HD void y4_ang_map(const V3 p, float &u, float &v)
+{
+	float r = xadd(xmul(p.x, p.x), xmul(p.z, p.z));
+	u = v = 0.f;
+	if(r > 0.f)
+	{
+		const float phi_ratio = (float) xdmul(Y4_1_PI, (Y4_WIDE) y4_acos(p.y));
+		r = xdiv(phi_ratio, xsqrt(r));
+		u = xmul(p.x, r);
+		v = xmul(p.z, r);
+	}
+}
+// TextureBackground::eval (background_texture.cc:44-78; no SmartIBL blur: refused on the host)
+Y4_HD C3 y4_texture_background(const Y4BgTex &B, const V3 dir)
+{
+	float u = 0.f, v = 0.f;
+	if(B.angular)
+	{
+		const V3 p = v3(xadd(xmul(dir.x, B.cos_r), xmul(dir.y, B.sin_r)), xadd(xmul(dir.x, -B.sin_r), xmul(dir.y, B.cos_r)), dir.z);
+		y4_ang_map(p, u, v);
+	}
+	else
+	{
+		y4_sphere_map(dir, u, v);
+		u = xsub(xmul(2.f, u), 1.f);
+		v = xsub(xmul(2.f, v), 1.f);
+		u = xadd(u, B.rotation);
+		if(u > 1.f) u = xsub(u, 2.f);
+	}
+	const C4 t = y4_tex_color(*B.tex, v3(u, v, 0.f));
+	C3 ret = c3(t.r, t.g, t.b);
+	const float min_component = 1.0e-5f;
+	if(ret.r < min_component) ret.r = min_component;
+	if(ret.g < min_component) ret.g = min_component;
+	if(ret.b < min_component) ret.b = min_component;
+	return cscale(ret, B.power);
+}
+// Rgb::clampProportionalRgb (color.h:415-447): the largest component goes to max_value, the others scale with it
+Y4_HD C3 y4_clamp_proportional(C3 c, float max_value)
+{
+	if(!(max_value > 0.f)) return c;
+	const float max_rgb = fmaxf(c.r, fmaxf(c.g, c.b));
+	const float adj = xdiv(max_value, max_rgb);
+	if(max_rgb > max_value)
+	{
+		if(c.r >= max_rgb) { c.r = max_value; c.g = xmul(c.g, adj); c.b = xmul(c.b, adj); }
+		else if(c.g >= max_rgb) { c.g = max_value; c.r = xmul(c.r, adj); c.b = xmul(c.b, adj); }
+		else { c.b = max_value; c.r = xmul(c.r, adj); c.g = xmul(c.g, adj); }
+	}
+	return c;
 }
 // BackgroundLight::calcFromSample / calcFromDir (:77-101)
 Y4_HD float y4_bg_from_sample(const Y4PtLight &L, float s1, float s2, float &u, float &v, bool inv)
@@ -659,7 +714,7 @@ Y4_HD bool y4_light_intersect(const Y4PtLight &L, const V3 from, const V3 dir, f
 	{
 		float u, v;
 		ipdf = y4_bg_from_dir(L, L.bg_abs_inter ? xneg(dir) : dir, u, v, true);
-		col = y4_bg_eval(L, y4_inv_sphere_map(u, v));
+		col = y4_clamp_proportional(y4_bg_eval(L, y4_inv_sphere_map(u, v)), L.bg_clamp);
 		t = -1.f;
 		return true;
 	}

@@ -75,6 +75,13 @@ struct Y4PtTexture
 	int checker_even, checker_odd; float checker_dist;
 	int adjustments_set, adj_clamp; float adj_intensity, adj_contrast, adj_red, adj_green, adj_blue;
 };
+// TextureBackground state (background_texture.cc:30-42): the image, the projection, rotation_ and its sine / cosine, power_
+struct Y4BgTex
+{
+	const Y4PtTexture *tex;
+	int angular;                    // mapping probe / angular: Texture::angMap, else Texture::sphereMap
+	float rotation, sin_r, cos_r, power;
+};
 // TextureMapperNode + LayerNode state of one layer of a diffuse_shader chain
 struct Y4PtLayer
 {
@@ -108,7 +115,9 @@ struct Y4PtLight
 	int bg_nv, bg_abs_inter;
 	const int *bg_off;          // [bg_nv + 2]
 	const float *bg_func, *bg_cdf, *bg_inv_int;     // bg_inv_int[y] = Pdf1D::invIntegral() of row y
-	int bg_gradient; C3 bg_col, bg_gz, bg_gh, bg_sz, bg_sh;     // the background itself (Background::eval)
+	int bg_gradient; C3 bg_col, bg_gz, bg_gh, bg_sz, bg_sh;     // the background itself (Background::eval); bg_gradient == 2: bg_tex
+	Y4BgTex bg_tex;
+	float bg_clamp;             // clamp_intersect_ (ibl_clamp_sampling of a textureback; 0: off)
 	float power;                // portal light: bg_->eval(dir) * power_
 };
 // Light::diracLight() / Light::canIntersect() of the supported lights (include/light/light_*.h)
@@ -129,6 +138,7 @@ struct Y4PtScene
 	                                // step), 2 shinydiffuse with a mirror component (one full estimate per ray level)
 	C3 background;
 	int bg_gradient; C3 bg_gz, bg_gh, bg_sz, bg_sh;     // gradientback: ground zenith / horizon, sky zenith / horizon
+	Y4BgTex bg_tex;                                     // bg_gradient == 2: textureback
 	float shadow_bias; int shadow_bias_auto;
 	float ray_min_dist; int ray_min_dist_auto;
 	uint32_t base_sampling_offset, rr_seed;

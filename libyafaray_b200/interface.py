@@ -270,13 +270,18 @@ class Interface:
 
     def createBackground(self, name):
         p = dict(self.params)
-        if p.get("type") not in ("constant", "gradientback"):
-            raise Y4Error("only constant / gradientback backgrounds are supported by the GPU back end")
+        if p.get("type") not in ("constant", "gradientback", "textureback"):
+            raise Y4Error("only constant / gradientback / textureback backgrounds are supported by the GPU back end")
+        if p["type"] == "textureback":                 # TextureBackground::factory (background_texture.cc:80-151)
+            if p.get("texture") not in self.textures:
+                raise Y4Error(f"textureback '{name}': texture '{p.get('texture')}' does not exist")
+            if float(p.get("smartibl_blur", 0.0)) > 0.0:
+                raise Y4Error("textureback: smartibl_blur (mip-mapped IBL lookups) is not supported by the GPU back end")
         self.backgrounds[name] = p
         if p.get("ibl", False):
-            # ConstantBackground::factory / GradientBackground::factory create the IBL light themselves, under a fixed name
-            # (background_constant.cc:58-69, background_gradient.cc:73-84); a second light of that name is refused by the scene
-            lname = "constantBackground_bgLight" if p["type"] == "constant" else "GradientBackground_bgLight"
+            # the background factories create the IBL light themselves, under a fixed name (background_constant.cc:58-69,
+            # background_gradient.cc:73-84, background_texture.cc:119-139); a second light of that name is refused by the scene
+            lname = {"constant": "constantBackground_bgLight", "gradientback": "GradientBackground_bgLight", "textureback": "textureBackground_bgLight"}[p["type"]]
             if lname not in self.lights:
                 self.lights[lname] = dict(type="bglight", samples=int(p.get("ibl_samples", 16)), cast_shadows=bool(p.get("cast_shadows", True)),
                                           _background=name)
@@ -547,6 +552,9 @@ class Interface:
                 if li == 0:
                     L.upper_color[:] = lay.get("upper_color", (0.0, 0.0, 0.0, 0.0))
                 layer_list.append(L)
+        if bg is not None and bg.get("type") == "textureback" and bg["texture"] not in tex_index:
+            tex_index[bg["texture"]] = len(tex_list)
+            tex_list.append(bg["texture"])
         textures = (_lib.PtTexture * max(1, len(tex_list)))()
         texel_arrays = []
         for i, tname in enumerate(tex_list):
@@ -675,6 +683,11 @@ class Interface:
                 pr.background_gradient = 1
                 for j, col in enumerate((gz, gh, sz, sh)):
                     pr.bg_gradient[j][:] = [float(np.float32(col[k]) * pw) for k in range(3)]
+            elif bg.get("type") == "textureback":
+                pr.background_gradient, pr.bg_texture = 2, tex_index[bg["texture"]]
+                pr.bg_texture_angular = int(str(bg.get("mapping", "")) in ("probe", "angular"))
+                pr.bg_texture_rotation, pr.bg_texture_power = float(bg.get("rotation", 0.0)), float(bg.get("power", 1.0))
+                pr.bg_ibl_clamp = float(bg.get("ibl_clamp_sampling", 0.0)) if bg.get("ibl", False) else 0.0
         if not rp.get("background_resampling", True):
             raise Y4Error("background_resampling=false is not supported by the GPU back end")
         pr.width, pr.height = int(rp.get("width", cam.resx)), int(rp.get("height", cam.resy))

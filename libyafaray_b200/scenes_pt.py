@@ -252,6 +252,21 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
     api.createCamera("cam")
 
     api.paramsClearAll()
+    if isinstance(background, dict) and "_image" in background:     # textureback: the image file and its texture come first
+        img = background["_image"]                                  # {"filename", "color_space", optional texture parameters}
+        api.paramsSetString("type", "image")
+        api.paramsSetString("filename", img["filename"])
+        api.paramsSetString("color_space", img.get("color_space", "LinearRGB"))
+        api.paramsSetFloat("gamma", 1.0)
+        api.paramsSetString("image_optimization", img.get("image_optimization", "none"))
+        api.createImage("bg_image")
+        api.paramsClearAll()
+        api.paramsSetString("type", "image")
+        api.paramsSetString("image_name", "bg_image")
+        _set_params(api, img.get("texture"))
+        api.createTexture(background.get("texture", "bg_tex"))
+        api.paramsClearAll()
+        background = {k: v for k, v in background.items() if k != "_image"}
     if isinstance(background, dict):    # another background type with its parameters, e.g. gradientback
         _set_params(api, background)
     else:

@@ -31,6 +31,8 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import helpers  # noqa: E402
 from libyafaray_b200 import scenes, scenes_pt  # noqa: E402
 
+TEST01_DIR = os.path.join(HERE, "test01")          # the reference's tests/test01 images (copied by make_golden.py)
+
 SOUP5M = dict(n_tri=5_000_000, n_rays=65536)
 SOUP50M = dict(n_tri=50_000_000, n_rays=65536)      # C5 at FULL size (needs ~30 GB of host memory and ~10 min for the kd-tree)
 CITY1M = dict(scene="city", n_tri_target=1_000_000, n_base=32, grid=48, tri_range=(1000, 8000), width=480, height=270, spp=2, bounces=8, filter_type="gauss")
@@ -238,6 +240,36 @@ def make_ao():
     np.savez_compressed(os.path.join(HERE, "pt_ao.npz"), **out)
 
 
+# textureback: an HDR image as the background (spherical / angular mapping, rotation, power), lighting the box as an IBL light
+# (with ibl_clamp_sampling) or through a portal -> pt_texback.npz
+_HDR = {"filename": "tex.hdr", "color_space": "LinearRGB"}
+_OUTSIDE = {"from": (0.5, 0.5, -0.6), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, -0.6)}
+PT_GOLDEN_TEXBACK = {
+    "texback_seen_spherical": dict(width=64, height=36, spp=3, bounces=2, camera_extra=dict(type="equirectangular", **_OUTSIDE),
+                                   background={"_image": _HDR, "type": "textureback", "texture": "bg_tex", "power": 1.5, "rotation": 40.0}),
+    "texback_seen_angular_nearest": dict(width=64, height=36, spp=2, bounces=2, camera_extra=dict(type="equirectangular", **_OUTSIDE),
+                                         background={"_image": dict(_HDR, texture={"interpolate": "none"}), "type": "textureback", "texture": "bg_tex",
+                                                     "mapping": "angular", "rotation": 75.0}),
+    "texback_ibl_path": dict(width=80, height=45, spp=3, bounces=3, lamp=False,
+                             background={"_image": _HDR, "type": "textureback", "texture": "bg_tex", "power": 12.0, "ibl": True, "ibl_samples": 3}),
+    "texback_ibl_clamp_direct": dict(width=80, height=45, spp=2, bounces=2, integrator="directlighting", lamp=False, filter_type="gauss",
+                                     background={"_image": _HDR, "type": "textureback", "texture": "bg_tex", "power": 15.0, "rotation": 200.0, "ibl": True,
+                                                 "ibl_samples": 4, "ibl_clamp_sampling": 2.5}),
+    "texback_portal": dict(width=80, height=45, spp=2, bounces=3, lamp=False, portal=1.5,
+                           background={"_image": _HDR, "type": "textureback", "texture": "bg_tex", "power": 10.0}),
+}
+
+
+def make_texback():
+    out = {}
+    for key, kw in PT_GOLDEN_TEXBACK.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec, cwd=TEST01_DIR)[0]
+        print(key, float(out[key][..., :3].mean()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_texback.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -272,6 +304,8 @@ if __name__ == "__main__":
         make_angular()
     if "ao" in what:
         make_ao()
+    if "texback" in what:
+        make_texback()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

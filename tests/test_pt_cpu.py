@@ -502,6 +502,26 @@ def test_ambient_occlusion_of_direct_lighting_vs_golden_reference_render(key):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+TEXBACK_KEYS = ["texback_seen_spherical", "texback_seen_angular_nearest", "texback_ibl_path", "texback_ibl_clamp_direct", "texback_portal"]
+
+
+@pytest.mark.parametrize("key", TEXBACK_KEYS)
+def test_texture_background_vs_golden_reference_render(key):
+    """textureback: an HDR image seen in every direction (Texture::sphereMap / angMap, rotation, power, the 1e-5 floor), as the
+    IBL light's energy table and colour (with ibl_clamp_sampling on the BSDF-sampled MIS half) and through a portal."""
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_TEXBACK
+    ref = np.load(os.path.join(GOLD, "pt_texback.npz"))[key]
+    a = _assemble(**PT_GOLDEN_TEXBACK[key])
+    assert a["params"].background_gradient == 2
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 def _shiny2_cfgs():
     sys.path.insert(0, GOLD)
     from make_golden_large import PT_GOLDEN_SHINY2
