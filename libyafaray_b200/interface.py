@@ -7,10 +7,11 @@ same names without the prefix, same argument order and meaning) -> Interface
 `paramsSet*` / `paramsClearAll` / `create*` are kept (interface.cc:118-197).  What the reference
 would render with `scene_accelerator = <kd-tree>` + `type = pathtracing` on CPU threads is rendered
 here by the BVH8 accelerator + wavefront path tracer kernels.  Scene features outside the supported
-set (shinydiffusemat without mirror/transparency, with an optional `diffuse_shader`
-chain of layer + texture_mapper nodes over image textures; light_mat; point/area/directional/sun/sphere/
-spot lights; perspective camera; constant background; pathtracing / directlighting) raise Y4Error --
-they are never approximated, and there is no CPU fallback.
+set (shinydiffusemat with all four components and an optional `diffuse_shader` chain of layer +
+texture_mapper nodes over image textures, light_mat, mirror, glass; point / area / directional / sun / sphere / spot /
+object / background (IBL) / background-portal lights; the five camera types; constant / gradient / image-texture
+backgrounds; pathtracing / directlighting with ambient occlusion; instances) raise Y4Error -- they are never
+approximated, and there is no CPU fallback.
 """
 from __future__ import annotations
 
