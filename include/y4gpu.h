@@ -207,6 +207,12 @@ typedef struct y4gpu_pt_material
 	float transmit_filter;        /* shinydiffusemat `transmit_filter` (default 1): share of the diffuse colour in that tint */
 	float translucency;           /* shinydiffusemat `translucency` (default 0): diffuse transmission to the other side */
 	int32_t reserved[3];
+	/* glass `absorption` / `absorption_dist` (GlassMaterial::factory, material_glass.cc:339-365): when a colour component is < 1 the
+	   material gets a Beer-Lambert volume handler (volumehandler_beer.cc) and every specular ray that continues INSIDE the glass has
+	   its radiance multiplied by exp(-sigma_a * hit distance) (integrator_montecarlo.cc:868-911; 0 when that ray leaves the scene) */
+	int32_t absorb;               /* 1: the handler exists */
+	float absorption[3];          /* `absorption` colour (components <= 1e-38 are not supported) */
+	double absorption_dist;       /* `absorption_dist` (default 1) */
 } y4gpu_pt_material;
 
 /* Image textures and the `diffuse_shader` node chains of shinydiffusemat: texture_mapper + layer nodes

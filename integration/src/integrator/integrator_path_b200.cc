@@ -220,7 +220,12 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 				// GlassMaterial::factory (material_glass.cc:290-433): IOR / transmit_filter / dispersion_power are double parameters
 				if(get<double>(p, "dispersion_power", 0.0) > 0.0 || get<bool>(p, "fake_shadows", false)) unsupported("glass '" + mat_names[i] + "': dispersion / fake_shadows");
 				const Rgb ab = getCol(p, "absorption", Rgb{1.f});
-				if(ab.r_ < 1.f || ab.g_ < 1.f || ab.b_ < 1.f) unsupported("glass '" + mat_names[i] + "': absorption");
+				if(ab.r_ < 1.f || ab.g_ < 1.f || ab.b_ < 1.f)      // material_glass.cc:339-365: a Beer-Lambert volume handler for the inside
+				{
+					if(ab.r_ <= 1e-38f || ab.g_ <= 1e-38f || ab.b_ <= 1e-38f) unsupported("glass '" + mat_names[i] + "': absorption colour with a zero component");
+					m.absorb = 1; put3(m.absorption, ab);
+					m.absorption_dist = get<double>(p, "absorption_dist", 1.0);
+				}
 				if(get<float>(p, "wireframe_amount", 0.f) != 0.f || get<float>(p, "samplingfactor", 1.f) != 1.f || get<int>(p, "additionaldepth", 0) != 0) unsupported("glass '" + mat_names[i] + "': wireframe / samplingfactor / additionaldepth");
 				for(const auto &kv : p) if(kv.first.size() > 7 && kv.first.compare(kv.first.size() - 7, 7, "_shader") == 0) unsupported("glass '" + mat_names[i] + "': shader nodes");
 				m.type = Y4GPU_MAT_GLASS;

@@ -51,7 +51,8 @@ class PtMaterial(C.Structure):
                 ("oren_nayar", C.c_int32), ("sigma", C.c_float), ("double_sided", C.c_int32), ("receive_shadows", C.c_int32),
                 ("flat_material", C.c_int32), ("layer_first", C.c_int32), ("layer_count", C.c_int32), ("specular_reflect", C.c_float),
                 ("mirror_color", C.c_float * 3), ("fresnel_effect", C.c_int32), ("ior", C.c_float), ("transparency", C.c_float), ("transmit_filter", C.c_float),
-                ("translucency", C.c_float), ("reserved", C.c_int32 * 3)]  # fmt: skip
+                ("translucency", C.c_float), ("reserved", C.c_int32 * 3),
+                ("absorb", C.c_int32), ("absorption", C.c_float * 3), ("absorption_dist", C.c_double)]  # fmt: skip
 
 
 class PtTexture(C.Structure):

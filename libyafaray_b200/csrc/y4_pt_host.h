@@ -122,6 +122,16 @@ inline Y4PtMaterial derive_material(const y4gpu_pt_material &m)
 		o.mirror_color = c3(m.mirror_color[0], m.mirror_color[1], m.mirror_color[2]);
 		o.ior = m.ior;
 		o.bsdf_flags = Y4_BSDF_SPECULAR | Y4_BSDF_REFLECT | Y4_BSDF_TRANSMIT;      // BsdfFlags::AllSpecular
+		if(m.absorb)                                       // BeerVolumeHandler ctor (volumehandler_beer.cc:27-35): std::log is this host's libm
+		{
+			o.absorb = 1;
+			o.sigma_a = c3(-logf(m.absorption[0]), -logf(m.absorption[1]), -logf(m.absorption[2]));
+			if(m.absorption_dist != 0.f)
+			{
+				const float inv = (float) (1.f / m.absorption_dist);      // "sigma_a_ *= 1.f / dist": a double quotient narrowed by Rgb::operator*=(float)
+				o.sigma_a = c3(o.sigma_a.r * inv, o.sigma_a.g * inv, o.sigma_a.b * inv);
+			}
+		}
 		return o;
 	}
 	o.color = c3(m.color[0], m.color[1], m.color[2]);

@@ -530,7 +530,7 @@ Y4_HD int y4_bounce_hit(const Y4PtScene &sc, const Y4PtWave &W, const Y4PtPass &
 	// tests/emu only: every estimateOneDirectLight call of the reference advances its counter, also the ones this
 	// function skips because they evaluate to exactly zero (non-diffuse vertex) or that Russian roulette discards later
 	// (the reference finishes all sub-paths of a ray level before it recurses: the level goes in front of the sub-path index)
-	const int lc_sub = sub + 4096 * ((f & Y4_PF_SPEC) ? (int) y4_f2u(ld4(W.sw, i).w) : 0);
+	const int lc_sub = sub + 4096 * ((f & Y4_PF_SPEC) ? (int) (y4_f2u(ld4(W.sw, i).w) & 0xffu) : 0);
 	if(sc.n_lights > 1 && (depth == 0 || (f & Y4_PF_DIFF1))) y4_test_light_choice_called(pix, samp, lc_sub, depth);
 #endif
 	if(depth == 0)
@@ -774,18 +774,23 @@ Y4_HD void y4_tree_fold(const Y4PtWave &W, uint32_t i, uint32_t &f, C3 rad)
 }
 // the vertex at (p, level) is done and has n_children (0..2) specular continuations; returns Y4_PUSH_SPEC while the
 // pixel-sample has a ray to trace, 0 when its tree is finished (then W.col / W.flags are what the splat expects)
-Y4_HD uint32_t y4_tree_next(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t f, int level, const V3 p, int n_children, const V3 *dir, const C3 *col)
+// med[k] != 0: child k continues inside an absorbing glass of material med[k] - 1; it travels in the upper bits of the level word
+// and is cashed in when the child's hit distance is known (y4_tree_medium)
+Y4_HD uint32_t y4_tree_next(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, uint32_t f, int level, const V3 p, int n_children, const V3 *dir, const C3 *col,
+                            const uint32_t *med = nullptr)
 {
 	const uint32_t n = W.n;
 	const bool has_sw = (f & Y4_PF_SPEC) != 0;
 	const C3 sw = has_sw ? ld3(W.sw, i) : c3f(1.f);
-	const float lvl = y4_u2f((uint32_t) (level + 1));
+	const uint32_t lvl_bits = (uint32_t) (level + 1);
+	const float lvl = y4_u2f(lvl_bits | ((med && n_children >= 1 ? med[0] : 0u) << 8));
+	const float lvl1 = y4_u2f(lvl_bits | ((med && n_children == 2 ? med[1] : 0u) << 8));
 	uint32_t k = W.stk_n[i];
 	if(n_children == 2)
 	{
 		const C3 w1 = has_sw ? cmul(sw, col[1]) : col[1];
 		st_ray(W.stk_ray, k * n + i, y4_mk_ray(p, sc.ray_min_dist, dir[1], -1.f));
-		st4(W.stk_sw, k * n + i, f4(w1.r, w1.g, w1.b, lvl));
+		st4(W.stk_sw, k * n + i, f4(w1.r, w1.g, w1.b, lvl1));
 		W.stk_n[i] = ++k;
 	}
 	if(n_children >= 1)
@@ -809,11 +814,29 @@ Y4_HD uint32_t y4_tree_next(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, 
 	W.flags[i] = f & Y4_PF_ACC;
 	return 0u;
 }
+// A tree ray that runs inside an absorbing glass: now that its hit is known, its branch weight takes BeerVolumeHandler::
+// transmittance (volumehandler_beer.cc:37-44: exp(-tmax * sigma_a) per channel with the FAST_MATH exp; 0 when the ray hit nothing,
+// tmax < 0).  The reference multiplies the finished radiance of the branch, here the weight carries the factor down: a few ulp.
+// Returns the ray level of the entry (the low byte of the level word; the medium tag is cleared).
+Y4_HD int y4_tree_medium(const Y4PtScene &sc, const Y4PtWave &W, uint32_t i, const Y4Hit &h)
+{
+	const float4 sw = ld4(W.sw, i);
+	const uint32_t word = y4_f2u(sw.w), med = word >> 8;
+	if(med)
+	{
+		const C3 sg = sc.mats[med - 1u].sigma_a;
+		C3 t = c3f(0.f);
+		if(h.prim >= 0 && !(h.t > 1e30f)) t = c3(y4_fast_exp(xmul(-h.t, sg.r)), y4_fast_exp(xmul(-h.t, sg.g)), y4_fast_exp(xmul(-h.t, sg.b)));
+		st4(W.sw, i, f4(xmul(sw.x, t.r), xmul(sw.y, t.g), xmul(sw.z, t.b), y4_u2f(word & 0xffu)));
+	}
+	return (int) (word & 0xffu);
+}
 // the specular continuations of a vertex: mirror, glass, shinydiffusemat (mirror and / or transparency component)
-Y4_HD int y4_tree_children(const Y4Vertex &vx, int level, V3 *dir, C3 *col)
+Y4_HD int y4_tree_children(const Y4Vertex &vx, int level, V3 *dir, C3 *col, uint32_t *med)
 {
 	const Y4PtMaterial &m = vx.m;
 	int nc = 0;
+	med[0] = med[1] = 0u;
 	if(m.type == Y4GPU_MAT_MIRROR)
 	{
 		dir[0] = y4_reflect_dir(y4_face_forward(vx.sp.ng, vx.sp.n, vx.wo), vx.wo); col[0] = m.color;     // MirrorMaterial::getSpecular
@@ -824,6 +847,8 @@ Y4_HD int y4_tree_children(const Y4Vertex &vx, int level, V3 *dir, C3 *col)
 		const Y4Specular s = y4_glass_specular(m, vx.sp, vx.wo, level + 1);
 		if(s.reflect) { dir[nc] = s.reflect_dir; col[nc] = s.reflect_col; ++nc; }
 		if(s.refract) { dir[nc] = s.refract_dir; col[nc] = s.refract_col; ++nc; }
+		// specularReflect / specularRefract: getVolumeHandler(sp.ng_ * ref_ray.dir_ < 0) -- the inside handler when the ray goes in
+		if(m.absorb) for(int k = 0; k < nc; ++k) if(xdot(vx.sp.ng, dir[k]) < 0.f) med[k] = vx.sp.mat + 1u;
 		return nc;
 	}
 	if(m.type != Y4GPU_MAT_SHINYDIFFUSE) return 0;
@@ -856,10 +881,10 @@ Y4_HD uint32_t y4_stage_primary3(const Y4PtScene &sc, const Y4PtWave &W, const Y
 {
 	uint32_t f = run > 0 ? (W.flags[i] & (uint32_t) (Y4_PF_SPEC | Y4_PF_ACC)) : 0u;
 	if(run == 0) W.stk_n[i] = 0u;
-	const int level = (f & Y4_PF_SPEC) ? (int) y4_f2u(ld4(W.sw, i).w) : 0;
 	const Y4Hit h = ld_hit(W.hit, i);
+	const int level = (f & Y4_PF_SPEC) ? y4_tree_medium(sc, W, i, h) : 0;
 	const Y4Ray r = (f & Y4_PF_SPEC) ? ld_ray(W.ray0, i) : ld_ray(W.ray, i);
-	V3 dir[2]; C3 col[2];
+	V3 dir[2]; C3 col[2]; uint32_t med[2];
 	if(h.prim < 0)
 	{
 		const bool invalid = !(f & Y4_PF_SPEC) && y4_camera_ray_invalid(r);
@@ -872,8 +897,8 @@ Y4_HD uint32_t y4_stage_primary3(const Y4PtScene &sc, const Y4PtWave &W, const Y
 	if(vx.m.type == Y4GPU_MAT_MIRROR || vx.m.type == Y4GPU_MAT_GLASS)
 	{
 		// no Diffuse, no Emit: integrate() returns recursiveRaytrace's share only
-		const int nc = deeper ? y4_tree_children(vx, level, dir, col) : 0;
-		return y4_tree_next(sc, W, i, f, level, vx.sp.p, nc, dir, col);
+		const int nc = deeper ? y4_tree_children(vx, level, dir, col, med) : 0;
+		return y4_tree_next(sc, W, i, f, level, vx.sp.p, nc, dir, col, med);
 	}
 	C3 c = c3f(0.f);
 	if(vx.m.bsdf_flags & Y4_BSDF_EMIT) c = cadd(c, y4_mat_emit(vx.m, vx.sp, vx.wo));
@@ -895,20 +920,20 @@ Y4_HD uint32_t y4_stage_finish3(const Y4PtScene &sc, const Y4PtWave &W, const Y4
 {
 	uint32_t f = W.flags[i];
 	const C3 rad = y4_level_radiance(sc, W, i, f, ld4(W.col, i));
-	const int level = (f & Y4_PF_SPEC) ? (int) y4_f2u(ld4(W.sw, i).w) : 0;
+	const int level = (f & Y4_PF_SPEC) ? (int) (y4_f2u(ld4(W.sw, i).w) & 0xffu) : 0;
 	const bool recurse = (f & Y4_PF_RECURSE) != 0;
 	uint32_t g = f & (uint32_t) (Y4_PF_SPEC | Y4_PF_ACC);
 	y4_tree_fold(W, i, g, rad);
-	V3 dir[2]; C3 col[2];
+	V3 dir[2]; C3 col[2]; uint32_t med[2] = {0u, 0u};
 	int nc = 0;
 	V3 p = v3(0.f, 0.f, 0.f);
 	if(recurse)
 	{
 		const Y4Vertex vx = y4_vertex<true>(sc, y4_level_ray<true>(sc, W, ps, i, f, W.pix[i], W.samp[i]), ld_hit(W.hit0, i));
-		nc = y4_tree_children(vx, level, dir, col);
+		nc = y4_tree_children(vx, level, dir, col, med);
 		p = vx.sp.p;
 	}
-	return y4_tree_next(sc, W, i, g, level, p, nc, dir, col);
+	return y4_tree_next(sc, W, i, g, level, p, nc, dir, col, med);
 }
 
 // ---- stage: close the pixel-sample and splat it into the film ----------------------------------------

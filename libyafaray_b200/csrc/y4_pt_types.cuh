@@ -63,6 +63,7 @@ struct Y4PtMaterial
 	int is_translucent; float translucency_strength;              // components_[2]: diffuse transmission
 	// glass (material_glass.cc): ior_, filter_color_ = filt * filter_color + (1 - filt) (kept in `color`), specular_reflection_color_ (in mirror_color)
 	float ior;
+	int absorb; C3 sigma_a;     // glass with `absorption`: BeerVolumeHandler::sigma_a_ of the inside volume handler
 };
 
 // ImageTexture state (texture_image.cc:476-597) + texels as Image::getColor returns them

@@ -243,9 +243,8 @@ class Interface:
                 raise Y4Error(f"glass '{name}': dispersion is not supported by the GPU back end")
             if p.get("fake_shadows", False):
                 raise Y4Error(f"glass '{name}': fake_shadows is not supported by the GPU back end")
-            ab = p.get("absorption", (1.0, 1.0, 1.0, 1.0))
-            if min(ab[:3]) < 1.0:
-                raise Y4Error(f"glass '{name}': absorption (a volume handler) is not supported by the GPU back end")
+            if min(p.get("absorption", (1.0, 1.0, 1.0, 1.0))[:3]) <= 1e-38:
+                raise Y4Error(f"glass '{name}': an absorption colour with a zero component is not supported by the GPU back end")
             if float(p.get("wireframe_amount", 0.0)) != 0.0 or float(p.get("samplingfactor", 1.0)) != 1.0 or int(p.get("additionaldepth", 0)) != 0:
                 raise Y4Error(f"glass '{name}': wireframe / samplingfactor / additionaldepth are not supported by the GPU back end")
             if any(k.endswith("_shader") for k in p):
@@ -593,6 +592,10 @@ class Interface:
                 fc = p.get("filter_color", (1.0, 1.0, 1.0, 1.0))
                 m.color[:] = [float(np.float32(np.float32(filt) * np.float32(fc[k])) + np.float32(1.0 - filt)) for k in range(3)]
                 m.mirror_color[:] = p.get("mirror_color", (1.0, 1.0, 1.0, 1.0))[:3]
+                ab = p.get("absorption", (1.0, 1.0, 1.0, 1.0))[:3]       # material_glass.cc:339-365: a Beer-Lambert handler for the inside
+                if min(np.float32(ab[k]) for k in range(3)) < 1.0:
+                    m.absorb, m.absorption_dist = 1, float(p.get("absorption_dist", 1.0))
+                    m.absorption[:] = [float(x) for x in ab]
             else:
                 m.type, m.diffuse_reflect, m.emit = _lib.MAT_SHINYDIFFUSE, float(p.get("diffuse_reflect", 1.0)), float(p.get("emit", 0.0))
                 m.specular_reflect, m.fresnel_effect, m.ior = float(p.get("specular_reflect", 0.0)), int(p.get("fresnel_effect", False)), float(p.get("IOR", 1.33))

@@ -120,6 +120,10 @@ def cornell_box(api, width=480, height=270, spp=16, bounces=8, path_samples=1, l
         api.paramsSetColor("filter_color", *glass.get("filter_color", (1.0, 1.0, 1.0)), 1.0)
         api.paramsSetFloat("transmit_filter", float(glass.get("transmit_filter", 0.0)))
         api.paramsSetColor("mirror_color", *glass.get("mirror_color", (1.0, 1.0, 1.0)), 1.0)
+        if "absorption" in glass:       # Beer-Lambert absorption inside the glass
+            api.paramsSetColor("absorption", *glass["absorption"], 1.0)
+            if "absorption_dist" in glass:
+                api.paramsSetFloat("absorption_dist", float(glass["absorption_dist"]))
         api.createMaterial("glass")
     mat = lambda obj, default: "mirror" if obj in mirrored else ("glass" if obj in glassy else default)
 

@@ -82,6 +82,29 @@ PT_GOLDEN_GLASS = {
 }
 
 
+# glass with `absorption`: the rays inside the glass are attenuated by exp(-sigma_a * distance) -> pt_glass_absorb.npz
+PT_GOLDEN_GLASS_ABSORB = {
+    "glass_absorb_sphere": dict(width=96, height=54, spp=3, bounces=3, smooth_sphere=30.0,
+                                glass={"objects": ("sphere",), "IOR": 1.5, "absorption": (0.3, 0.8, 0.5), "absorption_dist": 0.2}),
+    "glass_absorb_boxes_default_dist": dict(width=80, height=45, spp=2, bounces=3, box_lift=0.013, integrator_extra={"raydepth": 6},
+                                            glass={"objects": ("tall", "short"), "IOR": 1.6, "absorption": (0.9, 0.4, 0.7), "transmit_filter": 0.5,
+                                                   "filter_color": (1.0, 0.9, 0.8)}),
+    "glass_absorb_direct_gauss": dict(width=80, height=45, spp=2, bounces=2, integrator="directlighting", filter_type="gauss", smooth_sphere=30.0, box_lift=0.013,
+                                      glass={"objects": ("sphere", "tall"), "IOR": 1.45, "absorption": (0.6, 0.6, 0.95), "absorption_dist": 0.05},
+                                      background=(0.3, 0.4, 0.6)),
+}
+
+
+def make_glass_absorb():
+    out = {}
+    for key, kw in PT_GOLDEN_GLASS_ABSORB.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print(key, float(out[key][..., :3].mean()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_glass_absorb.npz"), **out)
+
+
 def make_glass():
     out = {}
     for key, kw in PT_GOLDEN_GLASS.items():
@@ -306,6 +329,8 @@ if __name__ == "__main__":
         make_ao()
     if "texback" in what:
         make_texback()
+    if "glass_absorb" in what:
+        make_glass_absorb()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

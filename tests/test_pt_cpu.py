@@ -522,6 +522,24 @@ def test_texture_background_vs_golden_reference_render(key):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+@pytest.mark.parametrize("key", ["glass_absorb_sphere", "glass_absorb_boxes_default_dist", "glass_absorb_direct_gauss"])
+def test_glass_absorption_vs_golden_reference_render(key):
+    """glass with `absorption`: the Beer-Lambert handler of the inside (sigma_a = -log(colour) / absorption_dist) attenuates every
+    specular ray that continues inside the glass by exp(-sigma_a * hit distance) (FAST_MATH exp), and blacks out one that leaves
+    the scene; the branch weight of the ray tree carries the factor."""
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_GLASS_ABSORB
+    ref = np.load(os.path.join(GOLD, "pt_glass_absorb.npz"))[key]
+    a = _assemble(**PT_GOLDEN_GLASS_ABSORB[key])
+    assert any(a["mats"][k].absorb for k in range(a["n_mat"]))
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 def _shiny2_cfgs():
     sys.path.insert(0, GOLD)
     from make_golden_large import PT_GOLDEN_SHINY2
