@@ -89,6 +89,10 @@ int y4gpu_create(int device, y4gpu_ctx **out);
 void y4gpu_destroy(y4gpu_ctx *ctx);
 const char *y4gpu_last_error(const y4gpu_ctx *ctx);   /* ctx may be NULL: last create error */
 int y4gpu_device_count(void);
+/* sizeof of the public structs as this library was compiled, for bindings that mirror them by hand (ctypes, cgo, JNI): index
+ * 0 build_params, 1 stats, 2 mesh, 3 instance, 4 pt_material, 5 pt_texture, 6 pt_layer, 7 pt_light, 8 pt_camera, 9 pt_params,
+ * 10 pt_stats, 11 pt_aa_noise, 12 ray, 13 hit, 14 tshit; 0 for any other index.  No GPU needed. */
+uint64_t y4gpu_struct_size(int which);
 
 /* Run all work of this ctx on the caller's CUDA stream (cudaStream_t passed as void*; NULL
  * restores the ctx's own non-blocking stream).  Lets a host application order the ctx's

@@ -143,7 +143,7 @@ _lib = None
 
 # every symbol include/y4gpu.h declares (checked by tests/test_cabi.py)
 EXPORTED = [
-    "y4gpu_create", "y4gpu_destroy", "y4gpu_last_error", "y4gpu_device_count",
+    "y4gpu_create", "y4gpu_destroy", "y4gpu_last_error", "y4gpu_device_count", "y4gpu_struct_size",
     "y4gpu_set_stream", "y4gpu_host_alloc", "y4gpu_host_free",
     "y4gpu_upload_triangles", "y4gpu_upload_instanced", "y4gpu_build", "y4gpu_get_bound",
     "y4gpu_trace", "y4gpu_trace_counted", "y4gpu_trace_tshadow", "y4gpu_trace_tshadow_inner", "y4gpu_trace_noalloc",
@@ -151,6 +151,10 @@ EXPORTED = [
     "y4gpu_pt_set_textures", "y4gpu_pt_set_scene", "y4gpu_pt_set_film_buffers", "y4gpu_pt_clear_film", "y4gpu_pt_render_pass",
     "y4gpu_pt_read_film", "y4gpu_pt_write_film", "y4gpu_pt_get_stats", "y4gpu_pt_next_pass", "y4gpu_libm_eval",
 ]  # fmt: skip
+
+
+# index = y4gpu_struct_size's argument (rays / hits travel as plain float arrays: no mirror)
+MIRRORED_STRUCTS = [BuildParams, Stats, Mesh, Instance, PtMaterial, PtTexture, PtLayer, PtLight, PtCamera, PtParams, PtStats, PtAaNoise, None, None, None]
 
 
 def lib() -> C.CDLL:
@@ -170,6 +174,13 @@ def lib() -> C.CDLL:
     L.y4gpu_last_error.restype = C.c_char_p
     L.y4gpu_device_count.argtypes = []
     L.y4gpu_device_count.restype = i32
+    L.y4gpu_struct_size.argtypes = [i32]
+    L.y4gpu_struct_size.restype = u64
+    # the ctypes mirrors above are written by hand: a library built from another header revision must not be driven with them
+    for which, cls in enumerate(MIRRORED_STRUCTS):
+        if cls is not None and C.sizeof(cls) != L.y4gpu_struct_size(which):
+            raise Y4Error(f"{LIB_PATH}: sizeof({cls.__name__}) is {L.y4gpu_struct_size(which)} in the library but {C.sizeof(cls)} in libyafaray_b200/_lib.py "
+                          "(rebuild: python -c 'import __graft_entry__ as g; g.build()')")
     L.y4gpu_set_stream.argtypes = [vp, vp]
     L.y4gpu_set_stream.restype = i32
     L.y4gpu_host_alloc.argtypes = [u64]

@@ -18,6 +18,14 @@ static bool is_device_ptr(const void *p)
 
 extern "C" {
 
+uint64_t y4gpu_struct_size(int which)
+{
+	static const uint64_t sizes[] = {sizeof(y4gpu_build_params), sizeof(y4gpu_stats), sizeof(y4gpu_mesh), sizeof(y4gpu_instance), sizeof(y4gpu_pt_material),
+	                                 sizeof(y4gpu_pt_texture), sizeof(y4gpu_pt_layer), sizeof(y4gpu_pt_light), sizeof(y4gpu_pt_camera), sizeof(y4gpu_pt_params),
+	                                 sizeof(y4gpu_pt_stats), sizeof(y4gpu_pt_aa_noise), sizeof(y4gpu_ray), sizeof(y4gpu_hit), sizeof(y4gpu_tshit)};
+	return which >= 0 && which < (int) (sizeof(sizes) / sizeof(sizes[0])) ? sizes[which] : 0;
+}
+
 int y4gpu_device_count(void)
 {
 	int n = 0;

@@ -26,6 +26,16 @@ def test_header_symbols_exported():
     assert sorted(_lib.EXPORTED) == names, "libyafaray_b200/_lib.py EXPORTED list out of sync with the header"
 
 
+def test_hand_written_struct_mirrors_have_the_sizes_the_library_was_compiled_with():
+    L = _lib.lib()          # (lib() itself refuses to load a library whose sizes differ)
+    sizes = [L.y4gpu_struct_size(k) for k in range(16)]
+    assert sizes[12:] == [32, 16, 32, 0] and all(s > 0 for s in sizes[:12])
+    for which, cls in enumerate(_lib.MIRRORED_STRUCTS):
+        if cls is not None:
+            assert C.sizeof(cls) == sizes[which], cls.__name__
+    assert L.y4gpu_struct_size(-1) == 0
+
+
 def test_no_cpu_fallback_without_gpu():
     L = _lib.lib()
     if L.y4gpu_device_count() > 0:
