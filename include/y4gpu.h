@@ -351,7 +351,8 @@ typedef struct y4gpu_pt_params
 	                                 (integrator_path_tracer.cc:227,256-264) */
 	int32_t transp_refracted_background;   /* bg_transp_refract (TiledIntegrator::background, integrator_tiled.cc:707-720) */
 	int32_t background_gradient;  /* 0: `constant` background (colour in `background`); 1: `gradientback` (background_gradient.cc:34-46);
-	                                 2: `textureback` (background_texture.cc), described by the bg_texture* fields below */
+	                                 2: `textureback` (background_texture.cc), described by the bg_texture* fields below;
+	                                 3: `sunsky` (background_sunsky.cc), described by the bg_sun_* fields below */
 	float bg_gradient[4][3];      /* gradientback colours * power: zenith_ground, horizon_ground, zenith, horizon */
 	/* ambient occlusion of the direct-lighting integrator (do_AO, AO_samples, AO_distance, AO_color; integrator_direct_light.cc:124,
 	   TiledIntegrator::sampleAmbientOcclusion, integrator_tiled.cc:644-692): after the lights, every diffuse vertex integrate() reaches
@@ -367,6 +368,12 @@ typedef struct y4gpu_pt_params
 	float bg_texture_power;       /* `power` */
 	float bg_ibl_clamp;           /* `ibl_clamp_sampling`: BackgroundLight::intersect clamps the colour proportionally (0: off).
 	                                 `smartibl_blur` (mip-mapped lookups for the light) is not supported: callers refuse it */
+	/* sunsky (SunSkyBackground::factory, background_sunsky.cc:226-307): Preetham daylight model.  `add_sun` is the caller's business
+	   (it creates an ordinary sunlight); `background_light` arrives as a Y4GPU_LIGHT_BACKGROUND like the other IBL lights */
+	float bg_sun_from[3];         /* `from`: direction towards the sun (default 1 1 1) */
+	float bg_sun_turbidity;       /* `turbidity` (default 4) */
+	float bg_sun_var[5];          /* `a_var` .. `e_var` (default 1) */
+	float bg_sun_power;           /* `power` (default 1) */
 } y4gpu_pt_params;
 
 typedef struct y4gpu_pt_stats

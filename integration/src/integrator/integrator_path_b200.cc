@@ -434,9 +434,18 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 			const ParamMap *bp = background_params;
 			if(!bp) unsupported("background without recorded parameters");
 			const std::string btype = getStr(*bp, "type");
-			if(btype != "constant" && btype != "gradientback" && btype != "textureback") unsupported("backgrounds other than constant / gradientback / textureback");
-			rendered_background_has_ibl = get<bool>(*bp, "ibl", false);
-			ibl_light_name = btype == "constant" ? "constantBackground_bgLight" : (btype == "gradientback" ? "GradientBackground_bgLight" : "textureBackground_bgLight");
+			if(btype != "constant" && btype != "gradientback" && btype != "textureback" && btype != "sunsky") unsupported("backgrounds other than constant / gradientback / textureback / sunsky");
+			rendered_background_has_ibl = get<bool>(*bp, btype == "sunsky" ? "background_light" : "ibl", false);
+			ibl_light_name = btype == "constant" ? "constantBackground_bgLight" : (btype == "gradientback" ? "GradientBackground_bgLight" : (btype == "sunsky" ? "sunsky_bgLight" : "textureBackground_bgLight"));
+			if(btype == "sunsky")            // SunSkyBackground::factory (background_sunsky.cc:226-307); its add_sun light is an ordinary recorded sunlight
+			{
+				pr.background_gradient = 3;
+				put3(pr.bg_sun_from, getVec(*bp, "from", Vec3{1.f, 1.f, 1.f}));
+				pr.bg_sun_turbidity = get<float>(*bp, "turbidity", 4.f);
+				pr.bg_sun_var[0] = get<float>(*bp, "a_var", 1.f); pr.bg_sun_var[1] = get<float>(*bp, "b_var", 1.f); pr.bg_sun_var[2] = get<float>(*bp, "c_var", 1.f);
+				pr.bg_sun_var[3] = get<float>(*bp, "d_var", 1.f); pr.bg_sun_var[4] = get<float>(*bp, "e_var", 1.f);
+				pr.bg_sun_power = (float) get<double>(*bp, "power", 1.0);
+			}
 			if(btype == "textureback")       // TextureBackground::factory (background_texture.cc:80-151)
 			{
 				if(get<float>(*bp, "smartibl_blur", 0.f) > 0.f) unsupported("textureback with smartibl_blur");

@@ -101,7 +101,8 @@ class PtParams(C.Structure):
                 ("transp_refracted_background", C.c_int32), ("background_gradient", C.c_int32), ("bg_gradient", (C.c_float * 3) * 4),
                 ("ao_samples", C.c_int32), ("ao_distance", C.c_float), ("ao_color", C.c_float * 3),
                 ("bg_texture", C.c_int32), ("bg_texture_angular", C.c_int32), ("bg_texture_rotation", C.c_float), ("bg_texture_power", C.c_float),
-                ("bg_ibl_clamp", C.c_float)]  # fmt: skip
+                ("bg_ibl_clamp", C.c_float), ("bg_sun_from", C.c_float * 3), ("bg_sun_turbidity", C.c_float), ("bg_sun_var", C.c_float * 5),
+                ("bg_sun_power", C.c_float)]  # fmt: skip
 
 
 class PtStats(C.Structure):

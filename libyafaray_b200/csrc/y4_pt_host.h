@@ -341,11 +341,54 @@ inline Y4BgTex derive_texture_background(const y4gpu_pt_params &p, const Y4PtTex
 	return b;
 }
 
+// SunSkyBackground ctor (background_sunsky.cc:39-80) + the direction-independent half of perezFunction (:82-104).  Types as in the
+// reference: sun_dir_ is a float vector, the members are doubles, pi is a long double; std::tan(double) is this host's libm.
+inline Y4BgSunsky derive_sunsky(const y4gpu_pt_params &p)
+{
+	Y4BgSunsky s;
+	memset(&s, 0, sizeof(s));
+	const HV sun = normalized(hv(p.bg_sun_from));
+	const double a_var = p.bg_sun_var[0], b_var = p.bg_sun_var[1], c_var = p.bg_sun_var[2], d_var = p.bg_sun_var[3], e_var = p.bg_sun_var[4];
+	s.theta_s = (double) y4_acos(sun.z);
+	const double theta_2 = s.theta_s * s.theta_s, theta_3 = theta_2 * s.theta_s;
+	s.phi_s = (double) y4_libm_atan2f(sun.y, sun.x);
+	const double t = (double) p.bg_sun_turbidity, t_2 = (double) (p.bg_sun_turbidity * p.bg_sun_turbidity);      // t_2_ = turb * turb: a float product
+	const double chi = (double) ((long double) ((4.0 / 9.0 - t / 120.0)) * (3.1415926535897932384626433832795L - (long double) (2.0 * s.theta_s)));
+	s.zenith_Y = (4.0453 * t - 4.9710) * tan(chi) - 0.2155 * t + 2.4192;
+	s.zenith_Y *= 1000;
+	s.zenith_x = (0.00165 * theta_3 - 0.00375 * theta_2 + 0.00209 * s.theta_s) * t_2 +
+	             (-0.02903 * theta_3 + 0.06377 * theta_2 - 0.03202 * s.theta_s + 0.00394) * t +
+	             (0.11693 * theta_3 - 0.21196 * theta_2 + 0.06052 * s.theta_s + 0.25886);
+	s.zenith_y = (0.00275 * theta_3 - 0.00610 * theta_2 + 0.00317 * s.theta_s) * t_2 +
+	             (-0.04214 * theta_3 + 0.08970 * theta_2 - 0.04153 * s.theta_s + 0.00516) * t +
+	             (0.15346 * theta_3 - 0.26756 * theta_2 + 0.06670 * s.theta_s + 0.26688);
+	s.perez_Y[0] = (0.17872 * t - 1.46303) * a_var; s.perez_Y[1] = (-0.35540 * t + 0.42749) * b_var; s.perez_Y[2] = (-0.02266 * t + 5.32505) * c_var;
+	s.perez_Y[3] = (0.12064 * t - 2.57705) * d_var; s.perez_Y[4] = (-0.06696 * t + 0.37027) * e_var;
+	s.perez_x[0] = (-0.01925 * t - 0.25922) * a_var; s.perez_x[1] = (-0.06651 * t + 0.00081) * b_var; s.perez_x[2] = (-0.00041 * t + 0.21247) * c_var;
+	s.perez_x[3] = (-0.06409 * t - 0.89887) * d_var; s.perez_x[4] = (-0.00325 * t + 0.04517) * e_var;
+	s.perez_y[0] = (-0.01669 * t - 0.26078) * a_var; s.perez_y[1] = (-0.09495 * t + 0.00921) * b_var; s.perez_y[2] = (-0.00792 * t + 0.21023) * c_var;
+	s.perez_y[3] = (-0.04405 * t - 1.65369) * d_var; s.perez_y[4] = (-0.01092 * t + 0.05291) * e_var;
+	s.sin_theta_s = y4_fast_sin((float) s.theta_s); s.cos_theta_s = y4_fast_cos((float) s.theta_s);
+	s.night = (long double) s.theta_s > 0.5L * 3.1415926535897932384626433832795L;
+	s.nfade_sun = (double) (1.0L - ((long double) s.theta_s * 0.31830988618379067153776752674502872L - 0.5L) * 2.0L);
+	const double *lams[3] = {s.perez_x, s.perez_y, s.perez_Y};
+	double *dens[3] = {&s.den_x, &s.den_y, &s.den_Y};
+	for(int k = 0; k < 3; ++k)
+	{
+		const double *lam = lams[k];
+		const double e_1 = y4_sunsky_exp(lam[1]), e_2 = y4_sunsky_exp(lam[3] * s.theta_s);
+		*dens[k] = (1 + lam[0] * e_1) * (1 + lam[2] * e_2 + lam[4] * s.cos_theta_s * s.cos_theta_s);
+	}
+	s.power = p.bg_sun_power;
+	return s;
+}
+
 // the background a background / portal light evaluates (Background::eval): a copy of the render parameters' description
 // (tex: where the light finds the textureback's image -- a host copy while the IBL tables are derived, the device array after)
-inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p, const Y4PtTexture *tex = nullptr)
+inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p, const Y4PtTexture *tex = nullptr, const Y4BgSunsky *sun = nullptr)
 {
 	if(p.background_gradient == 2) { o.bg_tex = derive_texture_background(p, tex); o.bg_clamp = p.bg_ibl_clamp; }
+	o.bg_sun = sun;
 	o.bg_gradient = p.background_gradient;
 	o.bg_col = c3(p.background[0], p.background[1], p.background[2]);
 	o.bg_gz = c3(p.bg_gradient[0][0], p.bg_gradient[0][1], p.bg_gradient[0][2]); o.bg_gh = c3(p.bg_gradient[1][0], p.bg_gradient[1][1], p.bg_gradient[1][2]);
@@ -357,10 +400,10 @@ inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p, cons
 // where the light's pointers can reach them; the background's own description is copied into the light for eval().
 inline void derive_background_light(Y4PtLight &o, const y4gpu_pt_light &l, const y4gpu_pt_params &p,
                                     std::vector<int> &off, std::vector<float> &func, std::vector<float> &cdf, std::vector<float> &inv_int,
-                                    const Y4PtTexture *host_tex = nullptr)
+                                    const Y4PtTexture *host_tex = nullptr, const Y4BgSunsky *host_sun = nullptr)
 {
 	o.bg_abs_inter = l.double_sided;
-	derive_light_background(o, p, host_tex);
+	derive_light_background(o, p, host_tex, host_sun);
 	const int nv = 360, max_u = 720, min_u = 16;
 	o.bg_nv = nv;
 	off.clear(); func.clear(); cdf.clear(); inv_int.clear();

@@ -418,8 +418,10 @@ Y4_HD bool y4_light_illuminate(const Y4PtLight &L, const V3 p, Y4LSample &ls)
 // ---- background light (src/light/light_background.cc) ------------------------------------------------------------
 // ConstantBackground::eval / GradientBackground::eval (background_gradient.cc:34-46)
 Y4_HD C3 y4_texture_background(const Y4BgTex &B, const V3 dir);
+Y4_HD C3 y4_sunsky_background(const Y4BgSunsky &S, const V3 dir);
 Y4_HD C3 y4_bg_eval(const Y4PtLight &L, const V3 dir)
 {
+	if(L.bg_gradient == 3) return y4_sunsky_background(*L.bg_sun, dir);
 	if(L.bg_gradient == 2) return y4_texture_background(L.bg_tex, dir);
 	if(!L.bg_gradient) return L.bg_col;
 	float blend = dir.z;
@@ -512,6 +514,59 @@ Y4_HD C3 y4_texture_background(const Y4BgTex &B, const V3 dir)
 	if(ret.g < min_component) ret.g = min_component;
 	if(ret.b < min_component) ret.b = min_component;
 	return cscale(ret, B.power);
+}
+// SunSkyBackground::perezFunction (background_sunsky.cc:82-104).  The reference's math::exp / math::cos take float arguments:
+// the double operands are narrowed first, the float results widened again; everything else is double arithmetic (no contraction).
+// den = the direction-independent denominator (host).
+Y4_HD double y4_sunsky_exp(double e) { return e <= 230. ? (double) y4_fast_exp((float) e) : 7.7220185e99; }
+Y4_HD double y4_perez(const double *lam, double theta, double gamma, double lvz, double den)
+{
+	const double e_3 = y4_sunsky_exp(xddiv(lam[1], (double) y4_fast_cos((float) theta)));
+	const double e_4 = y4_sunsky_exp(xdmul(lam[3], gamma));
+	const float cg = y4_fast_cos((float) gamma);
+	const double num = xdmul(xdadd(1., xdmul(lam[0], e_3)), xdadd(xdadd(1., xdmul(lam[2], e_4)), xdmul(xdmul(lam[4], (double) cg), (double) cg)));
+	return xddiv(xdmul(lvz, num), den);
+}
+// SunSkyBackground::eval -> getSkyCol (background_sunsky.cc:115-170): Preetham / Shirley / Smits daylight model.  acos / atan2 are
+// the C library's single-precision routines (y4_libm.cuh), sin / cos / exp the FAST_TRIG / FAST_MATH ones.
+Y4_HD C3 y4_sunsky_background(const Y4BgSunsky &S, const V3 dir)
+{
+	const V3 iw = xnormalize(dir);
+	double hfade = 1., nfade = 1.;
+	double theta = (double) y4_acos(iw.z);
+	const double half_pi = (double) (0.5 * Y4_PI);
+	if(theta > half_pi)
+	{
+		hfade = xdsub(1.0, xdmul(xdsub(xdmul(theta, (double) Y4_1_PI), 0.5), 2.0));      // (long double in the reference: the last bit of a double may differ)
+		hfade = xdmul(xdmul(hfade, hfade), xdsub(3.0, xdmul(2.0, hfade)));
+		theta = half_pi;
+	}
+	if(S.night && theta <= half_pi)
+	{
+		nfade = xdsub(1.0, xdmul(xdsub(0.5, xdmul(theta, (double) Y4_1_PI)), 2.0));
+		nfade = xdmul(nfade, S.nfade_sun);
+		nfade = xdmul(xdmul(nfade, nfade), xdsub(3.0, xdmul(2.0, nfade)));
+	}
+	double phi;
+	if(iw.y == 0.f && iw.x == 0.f) phi = half_pi;
+	else phi = (double) y4_libm_atan2f(iw.y, iw.x);
+	// angleBetween: the trigonometric terms are floats, so is their sum of products
+	const float cospsi = xadd(xmul(xmul(y4_fast_sin((float) theta), S.sin_theta_s), y4_fast_cos((float) xdsub(S.phi_s, phi))), xmul(y4_fast_cos((float) theta), S.cos_theta_s));
+	double gamma;
+	if(cospsi > 1.f) gamma = 0.;
+	else if(cospsi < -1.f) gamma = (double) Y4_PI;
+	else gamma = (double) y4_acos(cospsi);
+	const double x = y4_perez(S.perez_x, theta, gamma, S.zenith_x, S.den_x);
+	const double y = y4_perez(S.perez_y, theta, gamma, S.zenith_y, S.den_y);
+	const double Y = xdmul(xdmul(xdmul(6.666666667e-5, nfade), hfade), y4_perez(S.perez_Y, theta, gamma, S.zenith_Y, S.den_Y));
+	if(y == 0.) return c3f(0.f);
+	const double X = xdmul(xddiv(x, y), Y);
+	const double z = xdmul(xddiv(xdsub(xdsub(1.0, x), y), y), Y);
+	C3 c = c3((float) xdsub(xdsub(xdmul(3.240479, X), xdmul(1.537150, Y)), xdmul(0.498535, z)),
+	          (float) xdadd(xdadd(xdmul(-0.969256, X), xdmul(1.875992, Y)), xdmul(0.041556, z)),
+	          (float) xdadd(xdsub(xdmul(0.055648, X), xdmul(0.204043, Y)), xdmul(1.057311, z)));
+	c.r = fmaxf(0.f, fminf(1.f, c.r)); c.g = fmaxf(0.f, fminf(1.f, c.g)); c.b = fmaxf(0.f, fminf(1.f, c.b));      // clampRgb01
+	return cscale(c, S.power);
 }
 // Rgb::clampProportionalRgb (color.h:415-447): the largest component goes to max_value, the others scale with it
 Y4_HD C3 y4_clamp_proportional(C3 c, float max_value)

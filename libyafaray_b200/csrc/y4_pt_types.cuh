@@ -83,6 +83,19 @@ struct Y4BgTex
 	int angular;                    // mapping probe / angular: Texture::angMap, else Texture::sphereMap
 	float rotation, sin_r, cos_r, power;
 };
+// SunSkyBackground state (background_sunsky.cc:39-80) reduced to what eval() reads per direction: the sun's angles, the Perez
+// coefficients, the zenith values and the direction-independent denominators of perezFunction
+struct Y4BgSunsky
+{
+	double theta_s, phi_s;
+	float sin_theta_s, cos_theta_s;     // math::sin / math::cos of theta_s_ (FAST_TRIG, float argument)
+	int night;                          // theta_s_ > pi / 2
+	double nfade_sun;                   // 1 - (theta_s_ / pi - 0.5) * 2: the sun's share of the night fade
+	double perez_x[5], perez_y[5], perez_Y[5];
+	double zenith_x, zenith_y, zenith_Y;
+	double den_x, den_y, den_Y;
+	float power;
+};
 // TextureMapperNode + LayerNode state of one layer of a diffuse_shader chain
 struct Y4PtLayer
 {
@@ -118,6 +131,7 @@ struct Y4PtLight
 	const float *bg_func, *bg_cdf, *bg_inv_int;     // bg_inv_int[y] = Pdf1D::invIntegral() of row y
 	int bg_gradient; C3 bg_col, bg_gz, bg_gh, bg_sz, bg_sh;     // the background itself (Background::eval); bg_gradient == 2: bg_tex
 	Y4BgTex bg_tex;
+	const Y4BgSunsky *bg_sun;   // bg_gradient == 3: sunsky
 	float bg_clamp;             // clamp_intersect_ (ibl_clamp_sampling of a textureback; 0: off)
 	float power;                // portal light: bg_->eval(dir) * power_
 };
@@ -140,6 +154,7 @@ struct Y4PtScene
 	C3 background;
 	int bg_gradient; C3 bg_gz, bg_gh, bg_sz, bg_sh;     // gradientback: ground zenith / horizon, sky zenith / horizon
 	Y4BgTex bg_tex;                                     // bg_gradient == 2: textureback
+	const Y4BgSunsky *bg_sun;                           // bg_gradient == 3: sunsky
 	float shadow_bias; int shadow_bias_auto;
 	float ray_min_dist; int ray_min_dist_auto;
 	uint32_t base_sampling_offset, rr_seed;

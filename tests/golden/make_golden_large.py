@@ -293,6 +293,34 @@ def make_texback():
     np.savez_compressed(os.path.join(HERE, "pt_texback.npz"), **out)
 
 
+# sunsky: the Preetham daylight model as the background (day, and night with the below-horizon / night fades), as an IBL light
+# (background_light) and through a portal -> pt_sunsky.npz
+PT_GOLDEN_SUNSKY = {
+    "sunsky_seen_day": dict(width=64, height=36, spp=3, bounces=2, camera_extra=dict(type="equirectangular", **_OUTSIDE),
+                            background={"type": "sunsky", "from": (0.4, 0.7, 0.6), "turbidity": 3.0, "power": 1.5}),
+    "sunsky_seen_night_variations": dict(width=64, height=36, spp=2, bounces=2, camera_extra=dict(type="equirectangular", **_OUTSIDE),
+                                         background={"type": "sunsky", "from": (0.8, -0.5, -0.15), "turbidity": 6.0, "a_var": 1.2, "b_var": 0.8, "c_var": 1.1,
+                                                     "d_var": 0.9, "e_var": 1.3}),
+    "sunsky_ibl_path": dict(width=80, height=45, spp=3, bounces=3, lamp=False,
+                            background={"type": "sunsky", "from": (0.3, -0.8, 0.5), "turbidity": 2.5, "power": 8.0, "background_light": True, "light_samples": 3}),
+    "sunsky_ibl_direct_with_sun_gauss": dict(width=80, height=45, spp=2, bounces=2, integrator="directlighting", lamp=False, filter_type="gauss", extra_lights=("sun",),
+                                             background={"type": "sunsky", "from": (-0.2, -0.9, 0.4), "power": 5.0, "background_light": True, "light_samples": 4,
+                                                         "cast_shadows": False}),
+    "sunsky_portal": dict(width=80, height=45, spp=2, bounces=3, lamp=False, portal=1.5,
+                          background={"type": "sunsky", "from": (0.1, -0.6, 0.8), "turbidity": 4.0, "power": 6.0}),
+}
+
+
+def make_sunsky():
+    out = {}
+    for key, kw in PT_GOLDEN_SUNSKY.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print(key, float(out[key][..., :3].mean()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_sunsky.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -331,6 +359,8 @@ if __name__ == "__main__":
         make_texback()
     if "glass_absorb" in what:
         make_glass_absorb()
+    if "sunsky" in what:
+        make_sunsky()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

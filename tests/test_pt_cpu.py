@@ -540,6 +540,26 @@ def test_glass_absorption_vs_golden_reference_render(key):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+SUNSKY_KEYS = ["sunsky_seen_day", "sunsky_seen_night_variations", "sunsky_ibl_path", "sunsky_ibl_direct_with_sun_gauss", "sunsky_portal"]
+
+
+@pytest.mark.parametrize("key", SUNSKY_KEYS)
+def test_sunsky_background_vs_golden_reference_render(key):
+    """sunsky: SunSkyBackground::eval per direction (float acos / atan2 of the C library, FAST_TRIG sin / cos, FAST_MATH exp, the
+    rest in double), seen directly by day and by night, tabulated for its `background_light`, and through a portal."""
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_SUNSKY
+    ref = np.load(os.path.join(GOLD, "pt_sunsky.npz"))[key]
+    a = _assemble(**PT_GOLDEN_SUNSKY[key])
+    assert a["params"].background_gradient == 3
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 def _shiny2_cfgs():
     sys.path.insert(0, GOLD)
     from make_golden_large import PT_GOLDEN_SHINY2
