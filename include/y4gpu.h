@@ -183,7 +183,7 @@ int y4gpu_synchronize(y4gpu_ctx *ctx);
  * Scene features outside the supported set are rejected with Y4GPU_ERR_UNSUPPORTED.            */
 
 enum { Y4GPU_MAT_SHINYDIFFUSE = 0, Y4GPU_MAT_LIGHT = 1,
-       Y4GPU_MAT_GLASS = 3,      /* `glass` (GlassMaterial, src/material/material_glass.cc:35-433) without dispersion, absorption and fake shadows:
+       Y4GPU_MAT_GLASS = 3,      /* `glass` (GlassMaterial, src/material/material_glass.cc:35-433) without dispersion and fake shadows (absorption: the fields at the end of y4gpu_pt_material):
                                     `IOR` (in ior), `mirror_color`, and in `color` the constructor's filter colour transmit_filter * filter_color + (1 - transmit_filter).  getSpecular returns a
                                     reflected AND a refracted ray: recursiveRaytrace (integrator_montecarlo.cc:918-968) becomes a tree, which the
                                     device walks depth first with a per-pixel-sample stack of pending (ray, weight) entries */
