@@ -352,7 +352,8 @@ typedef struct y4gpu_pt_params
 	int32_t transp_refracted_background;   /* bg_transp_refract (TiledIntegrator::background, integrator_tiled.cc:707-720) */
 	int32_t background_gradient;  /* 0: `constant` background (colour in `background`); 1: `gradientback` (background_gradient.cc:34-46);
 	                                 2: `textureback` (background_texture.cc), described by the bg_texture* fields below;
-	                                 3: `sunsky` (background_sunsky.cc), described by the bg_sun_* fields below */
+	                                 3: `sunsky` (background_sunsky.cc), described by the bg_sun_* fields below;
+	                                 4: `darksky` (background_darksky.cc): bg_sun_from / turbidity / var / power + the bg_dark_* fields */
 	float bg_gradient[4][3];      /* gradientback colours * power: zenith_ground, horizon_ground, zenith, horizon */
 	/* ambient occlusion of the direct-lighting integrator (do_AO, AO_samples, AO_distance, AO_color; integrator_direct_light.cc:124,
 	   TiledIntegrator::sampleAmbientOcclusion, integrator_tiled.cc:644-692): after the lights, every diffuse vertex integrate() reaches
@@ -374,6 +375,13 @@ typedef struct y4gpu_pt_params
 	float bg_sun_turbidity;       /* `turbidity` (default 4) */
 	float bg_sun_var[5];          /* `a_var` .. `e_var` (default 1) */
 	float bg_sun_power;           /* `power` (default 1) */
+	/* darksky (DarkSkyBackground::factory, background_darksky.cc:194-314): the same model with altitude, exposure, a colour-space
+	   matrix, gamma encoding and a night mode (which halves `bright`: the caller passes the parameter as given) */
+	float bg_dark_altitude;       /* `altitude` (default 0) */
+	float bg_dark_bright;         /* `bright` (default 1) */
+	float bg_dark_exposure;       /* `exposure` (default 1) */
+	int32_t bg_dark_night;        /* `night` */
+	int32_t bg_dark_color_space;  /* `color_space`: 0 "CIE (E)" (default, also for unknown names), 1 "CIE (D50)", 2 "sRGB (D65)", 3 "sRGB (D50)" */
 } y4gpu_pt_params;
 
 typedef struct y4gpu_pt_stats

@@ -434,17 +434,26 @@ bool PathIntegratorB200::preprocess(ImageFilm *image_film, const RenderView *ren
 			const ParamMap *bp = background_params;
 			if(!bp) unsupported("background without recorded parameters");
 			const std::string btype = getStr(*bp, "type");
-			if(btype != "constant" && btype != "gradientback" && btype != "textureback" && btype != "sunsky") unsupported("backgrounds other than constant / gradientback / textureback / sunsky");
-			rendered_background_has_ibl = get<bool>(*bp, btype == "sunsky" ? "background_light" : "ibl", false);
-			ibl_light_name = btype == "constant" ? "constantBackground_bgLight" : (btype == "gradientback" ? "GradientBackground_bgLight" : (btype == "sunsky" ? "sunsky_bgLight" : "textureBackground_bgLight"));
-			if(btype == "sunsky")            // SunSkyBackground::factory (background_sunsky.cc:226-307); its add_sun light is an ordinary recorded sunlight
+			const bool sky = btype == "sunsky" || btype == "darksky";
+			if(btype != "constant" && btype != "gradientback" && btype != "textureback" && !sky) unsupported("background type '" + btype + "'");
+			rendered_background_has_ibl = get<bool>(*bp, sky ? "background_light" : "ibl", false);
+			ibl_light_name = btype == "constant" ? "constantBackground_bgLight" : (btype == "gradientback" ? "GradientBackground_bgLight" :
+			                 (btype == "sunsky" ? "sunsky_bgLight" : (btype == "darksky" ? "DarkSky_bgLight" : "textureBackground_bgLight")));
+			if(btype == "darksky")           // DarkSkyBackground::factory (background_darksky.cc:194-314)
 			{
-				pr.background_gradient = 3;
+				static const std::map<std::string, int> spaces{{"CIE (E)", 0}, {"CIE (D50)", 1}, {"sRGB (D65)", 2}, {"sRGB (D50)", 3}};
+				pr.bg_dark_altitude = get<float>(*bp, "altitude", 0.f); pr.bg_dark_bright = get<float>(*bp, "bright", 1.f);
+				pr.bg_dark_exposure = get<float>(*bp, "exposure", 1.f); pr.bg_dark_night = get<bool>(*bp, "night", false) ? 1 : 0;
+				pr.bg_dark_color_space = lookup(spaces, getStr(*bp, "color_space", "CIE (E)"), 0);
+			}
+			if(sky)                          // SunSkyBackground::factory (background_sunsky.cc:226-307); an add_sun light is an ordinary recorded sunlight
+			{
+				pr.background_gradient = btype == "sunsky" ? 3 : 4;
 				put3(pr.bg_sun_from, getVec(*bp, "from", Vec3{1.f, 1.f, 1.f}));
 				pr.bg_sun_turbidity = get<float>(*bp, "turbidity", 4.f);
 				pr.bg_sun_var[0] = get<float>(*bp, "a_var", 1.f); pr.bg_sun_var[1] = get<float>(*bp, "b_var", 1.f); pr.bg_sun_var[2] = get<float>(*bp, "c_var", 1.f);
 				pr.bg_sun_var[3] = get<float>(*bp, "d_var", 1.f); pr.bg_sun_var[4] = get<float>(*bp, "e_var", 1.f);
-				pr.bg_sun_power = (float) get<double>(*bp, "power", 1.0);
+				pr.bg_sun_power = btype == "sunsky" ? (float) get<double>(*bp, "power", 1.0) : get<float>(*bp, "power", 1.f);
 			}
 			if(btype == "textureback")       // TextureBackground::factory (background_texture.cc:80-151)
 			{

@@ -102,7 +102,8 @@ class PtParams(C.Structure):
                 ("ao_samples", C.c_int32), ("ao_distance", C.c_float), ("ao_color", C.c_float * 3),
                 ("bg_texture", C.c_int32), ("bg_texture_angular", C.c_int32), ("bg_texture_rotation", C.c_float), ("bg_texture_power", C.c_float),
                 ("bg_ibl_clamp", C.c_float), ("bg_sun_from", C.c_float * 3), ("bg_sun_turbidity", C.c_float), ("bg_sun_var", C.c_float * 5),
-                ("bg_sun_power", C.c_float)]  # fmt: skip
+                ("bg_sun_power", C.c_float), ("bg_dark_altitude", C.c_float), ("bg_dark_bright", C.c_float), ("bg_dark_exposure", C.c_float),
+                ("bg_dark_night", C.c_int32), ("bg_dark_color_space", C.c_int32)]  # fmt: skip
 
 
 class PtStats(C.Structure):
@@ -122,6 +123,7 @@ MAT_SHINYDIFFUSE, MAT_LIGHT, MAT_MIRROR, MAT_GLASS = 0, 1, 2, 3
 LIGHT_POINT, LIGHT_AREA, LIGHT_DIRECTIONAL, LIGHT_SUN, LIGHT_SPHERE, LIGHT_SPOT, LIGHT_OBJECT, LIGHT_BACKGROUND, LIGHT_SPOT_SOFT, LIGHT_PORTAL = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
 FILTERS = {"box": 0, "gauss": 1, "mitchell": 2, "lanczos": 3}
 CAMERA_TYPES = {"perspective": 0, "architect": 1, "orthographic": 2, "equirectangular": 3, "angular": 4}
+DARKSKY_COLOR_SPACES = {"CIE (E)": 0, "CIE (D50)": 1, "sRGB (D65)": 2, "sRGB (D50)": 3}
 ANGULAR_PROJECTIONS = {"equidistant": 0, "orthographic": 1, "stereographic": 2, "equisolid_angle": 3, "rectilinear": 4}
 BOKEH_TYPES = {"disk1": 0, "disk2": 1, "triangle": 3, "square": 4, "pentagon": 5, "hexagon": 6, "ring": 7}
 BOKEH_BIAS = {"uniform": 0, "center": 1, "edge": 2}

@@ -26,6 +26,7 @@ struct Y4Pt
 	uint32_t n_textures = 0, n_layers = 0;
 	std::vector<Y4PtTexture> h_textures;        // the descriptors as uploaded (texels = device pointers): a textureback looks its image up here
 	Y4BgSunsky *d_bg_sun = nullptr;             // sunsky background state (scene + lights point here)
+	Y4BgDarksky *d_bg_dark = nullptr;           // darksky background state
 	uint8_t *d_sigma = nullptr; uint16_t *d_offset = nullptr, *d_prime = nullptr; double *d_inv_prime = nullptr, *d_sigma_d = nullptr; unsigned long long *d_magic = nullptr;
 	bool scene_set = false;
 	y4gpu_pt_params params = {};
@@ -488,7 +489,7 @@ void y4gpu_pt_release(y4gpu_ctx *ctx)
 	if(pt->ev_fork) cudaEventDestroy(pt->ev_fork);
 	for(char *b : pt->light_blobs) cudaFree(b);
 	pt->light_blobs.clear();
-	cudaFree(pt->d_bg_sun);
+	cudaFree(pt->d_bg_sun); cudaFree(pt->d_bg_dark);
 	cudaFree(pt->d_mat_transp); cudaFree(pt->d_lights); cudaFree(pt->d_mats); cudaFree(pt->d_normals); cudaFree(pt->d_tri_shade);
 	pt_free_textures(pt);
 	cudaFree(pt->d_sigma); cudaFree(pt->d_offset); cudaFree(pt->d_prime); cudaFree(pt->d_inv_prime); cudaFree(pt->d_sigma_d); cudaFree(pt->d_magic);
@@ -660,7 +661,17 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 			bg_tex_host.texels = bg_texels_host.data();
 		}
 	}
-	else if(params->background_gradient < 0 || params->background_gradient > 3) { ctx->err = "unknown background type"; return Y4GPU_ERR_ARG; }
+	else if(params->background_gradient < 0 || params->background_gradient > 4) { ctx->err = "unknown background type"; return Y4GPU_ERR_ARG; }
+	Y4BgDarksky dark_host;
+	memset(&dark_host, 0, sizeof(dark_host));
+	if(params->background_gradient == 4)
+	{
+		dark_host = derive_darksky(*params);
+		if(!pt->d_bg_dark) Y4_CUDA(ctx, cudaMalloc(&pt->d_bg_dark, sizeof(Y4BgDarksky)));
+		Y4_CUDA(ctx, cudaMemcpyAsync(pt->d_bg_dark, &dark_host, sizeof(Y4BgDarksky), cudaMemcpyHostToDevice, st));
+		Y4_CUDA(ctx, cudaStreamSynchronize(st));
+		sc.bg_dark = pt->d_bg_dark;
+	}
 	// sunsky: the derived state lives in one small device block that the scene and the lights point to
 	Y4BgSunsky sun_host;
 	memset(&sun_host, 0, sizeof(sun_host));
@@ -688,7 +699,7 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 	for(uint32_t i = 0; i < n_light; ++i)
 	{
 		pt->h_lights[i] = derive_light(lights[i]);
-		if(lights[i].type == Y4GPU_LIGHT_PORTAL) derive_light_background(pt->h_lights[i], *params, pt->d_textures + (params->background_gradient == 2 ? params->bg_texture : 0), pt->d_bg_sun);
+		if(lights[i].type == Y4GPU_LIGHT_PORTAL) derive_light_background(pt->h_lights[i], *params, pt->d_textures + (params->background_gradient == 2 ? params->bg_texture : 0), pt->d_bg_sun, pt->d_bg_dark);
 		if(lights[i].type == Y4GPU_LIGHT_OBJECT || lights[i].type == Y4GPU_LIGHT_PORTAL)
 		{
 			// the light's own copy of its mesh: vertices, geometric normals, area cdf (ObjectLight::initIs) in one device block
@@ -711,9 +722,9 @@ int y4gpu_pt_set_scene(y4gpu_ctx *ctx, const y4gpu_pt_camera *cam, const y4gpu_p
 		{
 			// the tabulated background (BackgroundLight::init) in one device block: row offsets, function values, cdfs, 1 / integrals
 			std::vector<int> off; std::vector<float> func, cdf, inv_int;
-			derive_background_light(pt->h_lights[i], lights[i], *params, off, func, cdf, inv_int, &bg_tex_host, &sun_host);
+			derive_background_light(pt->h_lights[i], lights[i], *params, off, func, cdf, inv_int, &bg_tex_host, &sun_host, &dark_host);
 			if(params->background_gradient == 2) pt->h_lights[i].bg_tex.tex = pt->d_textures + params->bg_texture;      // from here on: the device copy
-			pt->h_lights[i].bg_sun = pt->d_bg_sun;
+			pt->h_lights[i].bg_sun = pt->d_bg_sun; pt->h_lights[i].bg_dark = pt->d_bg_dark;
 			const size_t b_off = off.size() * 4, b_f = func.size() * 4, b_i = inv_int.size() * 4;
 			char *blob = nullptr;
 			Y4_CUDA(ctx, cudaMalloc(&blob, b_off + 2 * b_f + b_i));

@@ -383,12 +383,63 @@ inline Y4BgSunsky derive_sunsky(const y4gpu_pt_params &p)
 	return s;
 }
 
+// DarkSkyBackground ctor + prePerez (background_darksky.cc:40-100,150-154) and the ColorConv matrices (color_conversion.h:58-81;
+// published XYZ -> RGB matrices).  std::exp / std::tan on doubles: this host's libm.
+inline Y4BgDarksky derive_darksky(const y4gpu_pt_params &p)
+{
+	Y4BgDarksky s;
+	memset(&s, 0, sizeof(s));
+	float bright = p.bg_dark_bright;
+	if(p.bg_dark_night) bright *= 0.5;
+	s.power = p.bg_sun_power * bright; s.bright = bright; s.alt = p.bg_dark_altitude; s.night = p.bg_dark_night; s.exposure = p.bg_dark_exposure;
+	static const float mats[4][9] = {
+		{2.3706743f, -0.9000405f, -0.4706338f, -0.5138850f, 1.4253036f, 0.0885814f, 0.0052982f, -0.0146949f, 1.0093968f},       // CIE RGB, illuminant E
+		{2.3638081f, -0.8676030f, -0.4988161f, -0.5005940f, 1.3962369f, 0.1047562f, 0.0141712f, -0.0306400f, 1.2323842f},       // CIE RGB, D50
+		{3.2404542f, -1.5371385f, -0.4985314f, -0.9692660f, 1.8760108f, 0.0415560f, 0.0556434f, -0.2040259f, 1.0572252f},       // sRGB, D65
+		{3.1338561f, -1.6168667f, -0.4906146f, -0.9787684f, 1.9161415f, 0.0334540f, 0.0719453f, -0.2289914f, 1.4052427f}};      // sRGB, D50
+	const int cs = p.bg_dark_color_space >= 0 && p.bg_dark_color_space < 4 ? p.bg_dark_color_space : 0;
+	for(int k = 0; k < 9; ++k) s.mat[k] = mats[cs][k];
+	HV sun = hv(p.bg_sun_from);
+	sun.z += s.alt;
+	sun = normalized(sun);
+	s.sun_dir = tov(sun);
+	const double theta_s = (double) y4_acos(sun.z);
+	const double cos_theta_s = (double) y4_fast_cos((float) theta_s);
+	const double cos_theta_2 = cos_theta_s * cos_theta_s;
+	const double theta_2 = theta_s * theta_s, theta_3 = theta_2 * theta_s;
+	const double t = (double) p.bg_sun_turbidity, t_2 = (double) (p.bg_sun_turbidity * p.bg_sun_turbidity);
+	const double av = p.bg_sun_var[0], bv = p.bg_sun_var[1], cv = p.bg_sun_var[2], dv = p.bg_sun_var[3], ev = p.bg_sun_var[4];
+	const double chi = (double) ((long double) (0.44444444 - (t / 120.0)) * (3.1415926535897932384626433832795L - (long double) (2.0 * theta_s)));
+	s.zenith_Y = (4.0453 * t - 4.9710) * tan(chi) - 0.2155 * t + 2.4192;
+	s.zenith_Y *= 1000;
+	s.zenith_x = (0.00165 * theta_3 - 0.00374 * theta_2 + 0.00209 * theta_s) * t_2 +
+	             (-0.02902 * theta_3 + 0.06377 * theta_2 - 0.03202 * theta_s + 0.00394) * t +
+	             (0.11693 * theta_3 - 0.21196 * theta_2 + 0.06052 * theta_s + 0.25885);
+	s.zenith_y = (0.00275 * theta_3 - 0.00610 * theta_2 + 0.00316 * theta_s) * t_2 +
+	             (-0.04214 * theta_3 + 0.08970 * theta_2 - 0.04153 * theta_s + 0.00515) * t +
+	             (0.15346 * theta_3 - 0.26756 * theta_2 + 0.06669 * theta_s + 0.26688);
+	s.perez_Y[0] = ((0.17872 * t) - 1.46303) * av; s.perez_Y[1] = ((-0.35540 * t) + 0.42749) * bv; s.perez_Y[2] = ((-0.02266 * t) + 5.32505) * cv;
+	s.perez_Y[3] = ((0.12064 * t) - 2.57705) * dv; s.perez_Y[4] = ((-0.06696 * t) + 0.37027) * ev;
+	s.perez_x[0] = ((-0.01925 * t) - 0.25922); s.perez_x[1] = ((-0.06651 * t) + 0.00081); s.perez_x[2] = ((-0.00041 * t) + 0.21247);
+	s.perez_x[3] = ((-0.06409 * t) - 0.89887); s.perez_x[4] = ((-0.00325 * t) + 0.04517);
+	s.perez_y[0] = ((-0.01669 * t) - 0.26078); s.perez_y[1] = ((-0.09495 * t) + 0.00921); s.perez_y[2] = ((-0.00792 * t) + 0.21023);
+	s.perez_y[3] = ((-0.04405 * t) - 1.65369); s.perez_y[4] = ((-0.01092 * t) + 0.05291);
+	double *lams[3] = {s.perez_Y, s.perez_x, s.perez_y};
+	for(double *lam : lams)
+	{
+		const double p_num = ((1 + lam[0] * exp(lam[1])) * (1 + (lam[2] * exp(lam[3] * theta_s)) + (lam[4] * cos_theta_2)));
+		lam[5] = p_num == 0.0 ? 0.0 : 1.0 / p_num;
+	}
+	return s;
+}
+
 // the background a background / portal light evaluates (Background::eval): a copy of the render parameters' description
 // (tex: where the light finds the textureback's image -- a host copy while the IBL tables are derived, the device array after)
-inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p, const Y4PtTexture *tex = nullptr, const Y4BgSunsky *sun = nullptr)
+inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p, const Y4PtTexture *tex = nullptr, const Y4BgSunsky *sun = nullptr,
+                                    const Y4BgDarksky *dark = nullptr)
 {
 	if(p.background_gradient == 2) { o.bg_tex = derive_texture_background(p, tex); o.bg_clamp = p.bg_ibl_clamp; }
-	o.bg_sun = sun;
+	o.bg_sun = sun; o.bg_dark = dark;
 	o.bg_gradient = p.background_gradient;
 	o.bg_col = c3(p.background[0], p.background[1], p.background[2]);
 	o.bg_gz = c3(p.bg_gradient[0][0], p.bg_gradient[0][1], p.bg_gradient[0][2]); o.bg_gh = c3(p.bg_gradient[1][0], p.bg_gradient[1][1], p.bg_gradient[1][2]);
@@ -400,10 +451,10 @@ inline void derive_light_background(Y4PtLight &o, const y4gpu_pt_params &p, cons
 // where the light's pointers can reach them; the background's own description is copied into the light for eval().
 inline void derive_background_light(Y4PtLight &o, const y4gpu_pt_light &l, const y4gpu_pt_params &p,
                                     std::vector<int> &off, std::vector<float> &func, std::vector<float> &cdf, std::vector<float> &inv_int,
-                                    const Y4PtTexture *host_tex = nullptr, const Y4BgSunsky *host_sun = nullptr)
+                                    const Y4PtTexture *host_tex = nullptr, const Y4BgSunsky *host_sun = nullptr, const Y4BgDarksky *host_dark = nullptr)
 {
 	o.bg_abs_inter = l.double_sided;
-	derive_light_background(o, p, host_tex, host_sun);
+	derive_light_background(o, p, host_tex, host_sun, host_dark);
 	const int nv = 360, max_u = 720, min_u = 16;
 	o.bg_nv = nv;
 	off.clear(); func.clear(); cdf.clear(); inv_int.clear();

@@ -208,6 +208,19 @@ Y4_HD float y4_fast_exp2(float x)
 	return xmul(expipart, y4_polyexp(fpart));
 }
 Y4_HD float y4_fast_exp(float a) { return y4_fast_exp2((float) (Y4_LOG2E * (Y4_WIDE) a)); }
+// math::log2 / math::pow with FAST_MATH (math.h:125-141,172-179): exponent bits + a degree-5 polynomial on the mantissa
+Y4_HD float y4_polylog(float x)
+{
+	return xadd(xmul(x, xadd(xmul(x, xadd(xmul(x, xadd(xmul(x, xadd(xmul(x, -3.4436006e-2f), 3.1821337e-1f)), -1.2315303f)), 2.5988452f)), -3.3241990f)), 3.1157899f);
+}
+Y4_HD float y4_fast_log2(float x)
+{
+	const uint32_t i = y4_f2u(x);
+	const float e = (float) ((int) ((i & 0x7F800000u) >> 23) - 127);
+	const float m = y4_u2f((i & 0x7FFFFFu) | 0x3F800000u);
+	return xadd(xmul(y4_polylog(m), xsub(m, 1.0f)), e);
+}
+Y4_HD float y4_fast_pow(float a, float b) { return y4_fast_exp2(xmul(y4_fast_log2(a), b)); }
 
 // ---- geometry helpers ----------------------------------------------------------------------------
 Y4_HD V3 xneg(V3 a) { return v3(-a.x, -a.y, -a.z); }

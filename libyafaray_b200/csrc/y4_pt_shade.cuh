@@ -419,8 +419,10 @@ Y4_HD bool y4_light_illuminate(const Y4PtLight &L, const V3 p, Y4LSample &ls)
 // ConstantBackground::eval / GradientBackground::eval (background_gradient.cc:34-46)
 Y4_HD C3 y4_texture_background(const Y4BgTex &B, const V3 dir);
 Y4_HD C3 y4_sunsky_background(const Y4BgSunsky &S, const V3 dir);
+Y4_HD C3 y4_darksky_background(const Y4BgDarksky &S, const V3 dir, bool with_power);
 Y4_HD C3 y4_bg_eval(const Y4PtLight &L, const V3 dir)
 {
+	if(L.bg_gradient == 4) return y4_darksky_background(*L.bg_dark, dir, true);        // lights call Background::eval
 	if(L.bg_gradient == 3) return y4_sunsky_background(*L.bg_sun, dir);
 	if(L.bg_gradient == 2) return y4_texture_background(L.bg_tex, dir);
 	if(!L.bg_gradient) return L.bg_col;
@@ -567,6 +569,50 @@ Y4_HD C3 y4_sunsky_background(const Y4BgSunsky &S, const V3 dir)
 	          (float) xdadd(xdsub(xdmul(0.055648, X), xdmul(0.204043, Y)), xdmul(1.057311, z)));
 	c.r = fmaxf(0.f, fminf(1.f, c.r)); c.g = fmaxf(0.f, fminf(1.f, c.g)); c.b = fmaxf(0.f, fminf(1.f, c.b));      // clampRgb01
 	return cscale(c, S.power);
+}
+// DarkSkyBackground::perezFunction (background_darksky.cc:156-160): double throughout, std::exp of the double C library.  The device
+// calls CUDA's exp() / acos(), whose results may differ from glibc's in the last bits of the double -- far below the float the
+// result is narrowed to right after (color_conv_.fromxyY takes floats); the host derives every constant with its own libm.
+Y4_HD double y4_dark_perez(const double *lam, double cos_theta, double gamma, double cos_gamma_2, double lvz)
+{
+	const double num = xdmul(xdadd(1., xdmul(lam[0], exp(xddiv(lam[1], cos_theta)))), xdadd(xdadd(1., xdmul(lam[2], exp(xdmul(lam[3], gamma)))), xdmul(lam[4], cos_gamma_2)));
+	return xdmul(xdmul(lvz, num), lam[5]);
+}
+// DarkSkyBackground::eval -> getSkyCol (:162-182) -> ColorConv::fromxyY (color_conversion.h:107-168; gamma encoding and clamping are
+// always on: the factory's constants).  with_power: eval() = getSkyCol * power_ (what the lights see); a ray that leaves the scene
+// calls the background's operator(), which DarkSkyBackground overrides WITHOUT power_ (:184-187)
+Y4_HD C3 y4_darksky_background(const Y4BgDarksky &S, const V3 dir, bool with_power)
+{
+	const V3 iw = xnormalize(v3(dir.x, dir.y, xadd(dir.z, S.alt)));
+	double cos_theta = (double) iw.z;
+	if(cos_theta <= 0.0) cos_theta = 1e-6;
+	const double cos_gamma = (double) xdot(iw, S.sun_dir);
+	const double cos_gamma_2 = xdmul(cos_gamma, cos_gamma);
+	const double gamma = acos(cos_gamma);
+	const float x = (float) y4_dark_perez(S.perez_x, cos_theta, gamma, cos_gamma_2, S.zenith_x);
+	const float y = (float) y4_dark_perez(S.perez_y, cos_theta, gamma, cos_gamma_2, S.zenith_y);
+	float Y = (float) xdmul(y4_dark_perez(S.perez_Y, cos_theta, gamma, cos_gamma_2, S.zenith_Y), 6.66666667e-5);
+	// fromxyY2Xyz
+	float X = 0.f, z = 0.f;
+	if(S.exposure > 0.f) Y = xsub(y4_fast_exp(xmul(Y, S.exposure)), 1.f);
+	if(y != 0.f)
+	{
+		const float ratio = xdiv(Y, y);
+		X = xmul(x, ratio);
+		z = xmul(xsub(xsub(1.f, x), y), ratio);
+	}
+	else Y = 0.f;
+	// fromXyz with sGammaEnc = math::pow(v, 1 / 2.2f), then clampRgb01
+	const float g = 1.f / 2.2f;
+	C3 c = c3(y4_fast_pow(xadd(xadd(xmul(S.mat[0], X), xmul(S.mat[1], Y)), xmul(S.mat[2], z)), g),
+	          y4_fast_pow(xadd(xadd(xmul(S.mat[3], X), xmul(S.mat[4], Y)), xmul(S.mat[5], z)), g),
+	          y4_fast_pow(xadd(xadd(xmul(S.mat[6], X), xmul(S.mat[7], Y)), xmul(S.mat[8], z)), g));
+	if(c.r < 0.f) c.r = 0.f; else if(c.r > 1.f) c.r = 1.f;
+	if(c.g < 0.f) c.g = 0.f; else if(c.g > 1.f) c.g = 1.f;
+	if(c.b < 0.f) c.b = 0.f; else if(c.b > 1.f) c.b = 1.f;
+	if(S.night) c = cmul(c, c3(0.05f, 0.05f, 0.08f));
+	c = cscale(c, S.bright);
+	return with_power ? cscale(c, S.power) : c;
 }
 // Rgb::clampProportionalRgb (color.h:415-447): the largest component goes to max_value, the others scale with it
 Y4_HD C3 y4_clamp_proportional(C3 c, float max_value)

@@ -281,6 +281,7 @@ Y4_HD Y4Vertex y4_vertex(const Y4PtScene &sc, const Y4Ray &r, const Y4Hit &h)
 // (*background)(ray.dir_): ConstantBackground::eval / GradientBackground::eval (background_gradient.cc:34-46)
 Y4_HD C3 y4_background(const Y4PtScene &sc, const V3 dir)
 {
+	if(sc.bg_gradient == 4) return y4_darksky_background(*sc.bg_dark, dir, false);      // DarkSkyBackground::operator() (background_darksky.cc:162-187): no power_
 	if(sc.bg_gradient == 3) return y4_sunsky_background(*sc.bg_sun, dir);       // SunSkyBackground::eval (background_sunsky.cc:115-175)
 	if(sc.bg_gradient == 2) return y4_texture_background(sc.bg_tex, dir);       // TextureBackground::eval (background_texture.cc:44-78)
 	if(!sc.bg_gradient) return sc.background;

@@ -96,6 +96,16 @@ struct Y4BgSunsky
 	double den_x, den_y, den_Y;
 	float power;
 };
+// DarkSkyBackground state (background_darksky.cc:40-100) + its ColorConv (color_conversion.h): the altitude-shifted sun direction,
+// the Perez coefficients with their pre-computed reciprocal denominators in [5], the zenith values, the XYZ -> RGB matrix
+struct Y4BgDarksky
+{
+	V3 sun_dir; float alt; int night;
+	double perez_x[6], perez_y[6], perez_Y[6];
+	double zenith_x, zenith_y, zenith_Y;
+	float exposure, mat[9];
+	float bright, power;                // sky_brightness_, power_ = power * bright
+};
 // TextureMapperNode + LayerNode state of one layer of a diffuse_shader chain
 struct Y4PtLayer
 {
@@ -132,6 +142,7 @@ struct Y4PtLight
 	int bg_gradient; C3 bg_col, bg_gz, bg_gh, bg_sz, bg_sh;     // the background itself (Background::eval); bg_gradient == 2: bg_tex
 	Y4BgTex bg_tex;
 	const Y4BgSunsky *bg_sun;   // bg_gradient == 3: sunsky
+	const Y4BgDarksky *bg_dark; // bg_gradient == 4: darksky
 	float bg_clamp;             // clamp_intersect_ (ibl_clamp_sampling of a textureback; 0: off)
 	float power;                // portal light: bg_->eval(dir) * power_
 };
@@ -155,6 +166,7 @@ struct Y4PtScene
 	int bg_gradient; C3 bg_gz, bg_gh, bg_sz, bg_sh;     // gradientback: ground zenith / horizon, sky zenith / horizon
 	Y4BgTex bg_tex;                                     // bg_gradient == 2: textureback
 	const Y4BgSunsky *bg_sun;                           // bg_gradient == 3: sunsky
+	const Y4BgDarksky *bg_dark;                         // bg_gradient == 4: darksky
 	float shadow_bias; int shadow_bias_auto;
 	float ray_min_dist; int ray_min_dist_auto;
 	uint32_t base_sampling_offset, rr_seed;

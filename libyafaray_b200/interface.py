@@ -270,16 +270,16 @@ class Interface:
 
     def createBackground(self, name):
         p = dict(self.params)
-        if p.get("type") not in ("constant", "gradientback", "textureback", "sunsky"):
-            raise Y4Error("only constant / gradientback / textureback / sunsky backgrounds are supported by the GPU back end")
-        if p["type"] == "sunsky":                      # SunSkyBackground::factory (background_sunsky.cc:226-307)
+        if p.get("type") not in ("constant", "gradientback", "textureback", "sunsky", "darksky"):
+            raise Y4Error(f"background type '{p.get('type')}' does not exist")
+        if p["type"] in ("sunsky", "darksky"):         # SunSkyBackground::factory (background_sunsky.cc:226-307), DarkSkyBackground::factory (background_darksky.cc:194-314)
             if p.get("add_sun", False):
-                raise Y4Error("sunsky: add_sun (a sunlight coloured by the reference's solar spectrum tables) is not supported by the GPU back end; "
+                raise Y4Error(f"{p['type']}: add_sun (a sunlight coloured by the reference's solar spectrum tables) is not supported by the GPU back end; "
                               "create the sunlight explicitly")
             self.backgrounds[name] = p
-            if p.get("background_light", False) and "sunsky_bgLight" not in self.lights:
-                self.lights["sunsky_bgLight"] = dict(type="bglight", samples=int(p.get("light_samples", 8)), cast_shadows=bool(p.get("cast_shadows", True)),
-                                                     _background=name)
+            lname = "sunsky_bgLight" if p["type"] == "sunsky" else "DarkSky_bgLight"
+            if p.get("background_light", False) and lname not in self.lights:
+                self.lights[lname] = dict(type="bglight", samples=int(p.get("light_samples", 8)), cast_shadows=bool(p.get("cast_shadows", True)), _background=name)
             return True
         if p["type"] == "textureback":                 # TextureBackground::factory (background_texture.cc:80-151)
             if p.get("texture") not in self.textures:
@@ -696,8 +696,12 @@ class Interface:
                 pr.background_gradient = 1
                 for j, col in enumerate((gz, gh, sz, sh)):
                     pr.bg_gradient[j][:] = [float(np.float32(col[k]) * pw) for k in range(3)]
-            elif bg.get("type") == "sunsky":
-                pr.background_gradient = 3
+            elif bg.get("type") in ("sunsky", "darksky"):
+                pr.background_gradient = 3 if bg["type"] == "sunsky" else 4
+                if bg["type"] == "darksky":
+                    pr.bg_dark_altitude, pr.bg_dark_bright = float(bg.get("altitude", 0.0)), float(bg.get("bright", 1.0))
+                    pr.bg_dark_exposure, pr.bg_dark_night = float(bg.get("exposure", 1.0)), int(bool(bg.get("night", False)))
+                    pr.bg_dark_color_space = _lib.DARKSKY_COLOR_SPACES.get(str(bg.get("color_space", "CIE (E)")), 0)
                 pr.bg_sun_from[:] = bg.get("from", (1.0, 1.0, 1.0))[:3]
                 pr.bg_sun_turbidity, pr.bg_sun_power = float(bg.get("turbidity", 4.0)), float(bg.get("power", 1.0))
                 pr.bg_sun_var[:] = [float(bg.get(k, 1.0)) for k in ("a_var", "b_var", "c_var", "d_var", "e_var")]

@@ -5,7 +5,7 @@
 // call sequence can be replayed against libyafaray_b200.interface.Interface (our host-side mirror).
 //
 // usage: ref_render <scene.script>
-//   script commands (whitespace separated; names/strings contain no spaces):
+//   script commands (whitespace separated; names contain no spaces, a string value runs to the end of its line):
 //     paramsClearAll | paramsSetString n s | paramsSetBool n 0|1 | paramsSetInt n i | paramsSetFloat n f
 //     paramsSetVector n x y z | paramsSetColor n r g b a | paramsPushList | paramsEndList
 //     createMaterial|createLight|createCamera|createBackground|createIntegrator|createRenderView|createObject|createOutput name
@@ -77,7 +77,14 @@ int main(int argc, char **argv)
 		if(cmd == "paramsClearAll") yafaray_paramsClearAll(yi);
 		else if(cmd == "paramsPushList") yafaray_paramsPushList(yi);
 		else if(cmd == "paramsEndList") yafaray_paramsEndList(yi);
-		else if(cmd == "paramsSetString") { ss >> a >> b; yafaray_paramsSetString(yi, a.c_str(), b.c_str()); }
+		else if(cmd == "paramsSetString")      // the value is the rest of the line (e.g. color_space "CIE (D50)" has spaces)
+		{
+			ss >> a;
+			std::getline(ss, b);
+			const size_t first = b.find_first_not_of(" \t"), last = b.find_last_not_of(" \t\r");
+			b = first == std::string::npos ? std::string() : b.substr(first, last - first + 1);
+			yafaray_paramsSetString(yi, a.c_str(), b.c_str());
+		}
 		else if(cmd == "paramsSetBool") { int v; ss >> a >> v; yafaray_paramsSetBool(yi, a.c_str(), v ? YAFARAY_BOOL_TRUE : YAFARAY_BOOL_FALSE); }
 		else if(cmd == "paramsSetInt") { int v; ss >> a >> v; yafaray_paramsSetInt(yi, a.c_str(), v); }
 		else if(cmd == "paramsSetFloat") { double v; ss >> a >> v; yafaray_paramsSetFloat(yi, a.c_str(), v); }

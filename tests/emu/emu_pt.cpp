@@ -146,6 +146,8 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	}
 	static Y4BgSunsky sun;
 	if(params->background_gradient == 3) { sun = derive_sunsky(*params); sc.bg_sun = &sun; }
+	static Y4BgDarksky dark;
+	if(params->background_gradient == 4) { dark = derive_darksky(*params); sc.bg_dark = &dark; }
 	sc.shadow_bias = params->shadow_bias; sc.shadow_bias_auto = params->shadow_bias_auto;
 	sc.ray_min_dist = params->min_raydist; sc.ray_min_dist_auto = params->min_raydist_auto;
 	sc.base_sampling_offset = params->base_sampling_offset; sc.rr_seed = params->rr_seed;
@@ -159,7 +161,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 	static std::vector<std::vector<float>> obj_cdf, obj_tris; static std::vector<std::vector<float4>> obj_ng;     // object lights' mesh copies
 	obj_cdf.assign(n_light, {}); obj_tris.assign(n_light, {}); obj_ng.assign(n_light, {});
 	for(uint32_t i = 0; i < n_light; ++i) { hl[i] = derive_light(lights[i]);
-		if(lights[i].type == Y4GPU_LIGHT_PORTAL) derive_light_background(hl[i], *params, bg_tex, &sun);
+		if(lights[i].type == Y4GPU_LIGHT_PORTAL) derive_light_background(hl[i], *params, bg_tex, &sun, &dark);
 		if(lights[i].type == Y4GPU_LIGHT_OBJECT || lights[i].type == Y4GPU_LIGHT_PORTAL)
 		{
 			obj_tris[i].assign(lights[i].object_tris, lights[i].object_tris + 9ull * lights[i].object_n_tris);
@@ -169,7 +171,7 @@ extern "C" int emu_pt_render(const y4gpu_pt_camera *cam, const y4gpu_pt_material
 		if(lights[i].type == Y4GPU_LIGHT_BACKGROUND)
 		{
 			static std::vector<int> bg_off; static std::vector<float> bg_func, bg_cdf, bg_inv;     // (one background light per scene)
-			derive_background_light(hl[i], lights[i], *params, bg_off, bg_func, bg_cdf, bg_inv, bg_tex, &sun);
+			derive_background_light(hl[i], lights[i], *params, bg_off, bg_func, bg_cdf, bg_inv, bg_tex, &sun, &dark);
 			hl[i].bg_off = bg_off.data(); hl[i].bg_func = bg_func.data(); hl[i].bg_cdf = bg_cdf.data(); hl[i].bg_inv_int = bg_inv.data();
 		}
 		const int ns = y4_light_num_samples(sc, hl[i]); if(ns > max_ls) max_ls = ns; }

@@ -321,6 +321,35 @@ def make_sunsky():
     np.savez_compressed(os.path.join(HERE, "pt_sunsky.npz"), **out)
 
 
+# darksky: the same daylight model with altitude, exposure, colour-space matrix, gamma encoding and night mode -> pt_darksky.npz
+PT_GOLDEN_DARKSKY = {
+    "darksky_seen_day": dict(width=64, height=36, spp=3, bounces=2, camera_extra=dict(type="equirectangular", **_OUTSIDE),
+                             background={"type": "darksky", "from": (0.4, 0.7, 0.6), "turbidity": 3.0, "power": 1.2, "bright": 1.5}),
+    "darksky_seen_night_srgb_altitude": dict(width=64, height=36, spp=2, bounces=2, camera_extra=dict(type="equirectangular", **_OUTSIDE),
+                                             background={"type": "darksky", "from": (0.8, -0.5, 0.2), "turbidity": 5.0, "night": True, "altitude": 0.3,
+                                                         "exposure": 2.0, "color_space": "sRGB (D65)", "a_var": 1.2, "b_var": 0.8, "c_var": 1.1, "d_var": 0.9,
+                                                         "e_var": 1.3}),
+    "darksky_ibl_path": dict(width=80, height=45, spp=3, bounces=3, lamp=False,
+                             background={"type": "darksky", "from": (0.3, -0.8, 0.5), "turbidity": 2.5, "power": 4.0, "background_light": True, "light_samples": 3,
+                                         "color_space": "CIE (D50)"}),
+    "darksky_ibl_direct_no_exposure_gauss": dict(width=80, height=45, spp=2, bounces=2, integrator="directlighting", lamp=False, filter_type="gauss", extra_lights=("sun",),
+                                                 background={"type": "darksky", "from": (-0.2, -0.9, 0.4), "power": 3.0, "exposure": 0.0, "background_light": True,
+                                                             "light_samples": 4, "color_space": "sRGB (D50)"}),
+    "darksky_portal": dict(width=80, height=45, spp=2, bounces=3, lamp=False, portal=1.5,
+                           background={"type": "darksky", "from": (0.1, -0.6, 0.8), "turbidity": 4.0, "power": 5.0}),
+}
+
+
+def make_darksky():
+    out = {}
+    for key, kw in PT_GOLDEN_DARKSKY.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print(key, float(out[key][..., :3].mean()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_darksky.npz"), **out)
+
+
 RR_ON = dict(width=64, height=36, spp=1024, bounces=8, rr_min_bounces=0)     # the integrator's DEFAULT: Russian roulette from the first bounce
 
 
@@ -361,6 +390,8 @@ if __name__ == "__main__":
         make_glass_absorb()
     if "sunsky" in what:
         make_sunsky()
+    if "darksky" in what:
+        make_darksky()
     if "rr" in what:
         make_rr()
     if "soup50m" in what:

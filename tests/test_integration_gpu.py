@@ -20,7 +20,7 @@ ALL_GOLDEN = {**{k: ("pt_cornell.npz", v) for k, v in PT_GOLDEN.items()}, **{k: 
               **{k: ("pt_dof.npz", v) for k, v in PT_GOLDEN_DOF.items()}, **{k: ("pt_test01.npz", v) for k, v in PT_GOLDEN_TEST01.items()},
               **{k: ("pt_mirror.npz", v) for k, v in PT_GOLDEN_MIRROR.items()},
               **{k: ("pt_lights.npz", v) for k, v in PT_GOLDEN_LIGHTS.items() if v.get("integrator") == "directlighting" or not v.get("extra_lights")}}
-from make_golden_large import PT_GOLDEN_ANGULAR, PT_GOLDEN_AO, PT_GOLDEN_GLASS, PT_GOLDEN_GLASS_ABSORB, PT_GOLDEN_IBL, PT_GOLDEN_PORTAL, PT_GOLDEN_SHINY2, PT_GOLDEN_SPOT_SOFT, PT_GOLDEN_SUNSKY, PT_GOLDEN_TEXBACK  # noqa: E402
+from make_golden_large import PT_GOLDEN_ANGULAR, PT_GOLDEN_AO, PT_GOLDEN_DARKSKY, PT_GOLDEN_GLASS, PT_GOLDEN_GLASS_ABSORB, PT_GOLDEN_IBL, PT_GOLDEN_PORTAL, PT_GOLDEN_SHINY2, PT_GOLDEN_SPOT_SOFT, PT_GOLDEN_SUNSKY, PT_GOLDEN_TEXBACK  # noqa: E402
 
 ALL_GOLDEN.update({k: ("pt_glass.npz", v) for k, v in PT_GOLDEN_GLASS.items()})
 ALL_GOLDEN.update({k: ("pt_shiny2.npz", v) for k, v in PT_GOLDEN_SHINY2.items()})
@@ -31,6 +31,7 @@ ALL_GOLDEN.update({k: ("pt_ao.npz", v) for k, v in PT_GOLDEN_AO.items()})
 ALL_GOLDEN.update({k: ("pt_texback.npz", v) for k, v in PT_GOLDEN_TEXBACK.items()})
 ALL_GOLDEN.update({k: ("pt_glass_absorb.npz", v) for k, v in PT_GOLDEN_GLASS_ABSORB.items()})
 ALL_GOLDEN.update({k: ("pt_sunsky.npz", v) for k, v in PT_GOLDEN_SUNSKY.items()})
+ALL_GOLDEN.update({k: ("pt_darksky.npz", v) for k, v in PT_GOLDEN_DARKSKY.items()})
 ALL_GOLDEN.update({k: ("pt_ibl.npz", v) for k, v in PT_GOLDEN_IBL.items() if k != "ibl_path_with_lamp"})
 PSNR_MIN = 50.0
 

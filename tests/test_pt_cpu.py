@@ -560,6 +560,26 @@ def test_sunsky_background_vs_golden_reference_render(key):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+DARKSKY_KEYS = ["darksky_seen_day", "darksky_seen_night_srgb_altitude", "darksky_ibl_path", "darksky_ibl_direct_no_exposure_gauss", "darksky_portal"]
+
+
+@pytest.mark.parametrize("key", DARKSKY_KEYS)
+def test_darksky_background_vs_golden_reference_render(key):
+    """darksky: DarkSkyBackground::eval per direction (double Perez functions, ColorConv::fromxyY with exposure, the four XYZ -> RGB
+    matrices, FAST_MATH gamma encoding, clamping, night tint), seen directly, tabulated for its `background_light`, through a portal."""
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_DARKSKY
+    ref = np.load(os.path.join(GOLD, "pt_darksky.npz"))[key]
+    a = _assemble(**PT_GOLDEN_DARKSKY[key])
+    assert a["params"].background_gradient == 4
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.005
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 def _shiny2_cfgs():
     sys.path.insert(0, GOLD)
     from make_golden_large import PT_GOLDEN_SHINY2
