@@ -191,6 +191,50 @@ def test_interface_rejects_unsupported_features():
         yi.setupRender()
 
 
+def test_round_two_features_keep_refusing_what_they_do_not_restate():
+    """The corners of the newer features that are NOT restated: refused with Y4Error, never approximated."""
+    yi = interface.Interface()
+    yi.image_dir = TEST01_DIR
+    for bad in (dict(type="textureback", texture="nowhere"),                       # TextureBackground::factory: texture must exist
+                dict(type="sunsky", add_sun=True), dict(type="darksky", add_sun=True),   # sunlight colour from the solar spectrum tables
+                dict(type="clouds_sky")):
+        yi.paramsClearAll()
+        scenes_pt._set_params(yi, bad)
+        with pytest.raises(Y4Error):
+            yi.createBackground("bg")
+    yi.paramsClearAll()
+    yi.paramsSetString("filename", "tex.hdr")
+    assert yi.createImage("img")
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="image", image_name="img"))
+    assert yi.createTexture("sky")
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="textureback", texture="sky", smartibl_blur=0.3))     # mip-mapped IBL lookups
+    with pytest.raises(Y4Error):
+        yi.createBackground("bg")
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="textureback", texture="sky", ibl=True))
+    assert yi.createBackground("bg") and "textureBackground_bgLight" in yi.lights
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="darksky", background_light=True, light_samples=5))
+    assert yi.createBackground("sky2") and yi.lights["DarkSky_bgLight"]["samples"] == 5
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="directlighting", do_AO=True, AO_samples=0))          # the reference divides by zero
+    with pytest.raises(Y4Error):
+        yi.createIntegrator("i")
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="pathtracing", do_AO=True))                           # parsed and ignored by the reference's path tracer
+    assert yi.createIntegrator("i")
+    yi.paramsClearAll()
+    yi.paramsSetString("type", "glass")
+    yi.paramsSetColor("absorption", 0.5, 0.0, 0.5, 1.0)                                       # -log(0): the reference falls back to log(1e38)
+    with pytest.raises(Y4Error):
+        yi.createMaterial("g")
+    yi.paramsClearAll()
+    scenes_pt._set_params(yi, dict(type="angular", projection="no_such_projection"))          # unknown names select equidistant, like the factory
+    assert yi.createCamera("c")
+
+
 def test_texture_features_outside_the_supported_set_are_rejected_or_dropped_like_the_reference():
     yi = interface.Interface()
     yi.image_dir = TEST01_DIR
