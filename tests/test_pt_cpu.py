@@ -314,7 +314,10 @@ def test_lens_shapes_vs_live_reference(bokeh):
 
 
 CAMERAS = [dict(type="orthographic", scale=1.3), dict(type="architect", focal=1.1), dict(type="architect", aperture=0.05, dof_distance=1.8, bokeh_type="square"),
-           dict(type="equirectangular", **{"from": (0.5, 0.5, 0.3), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, 0.3)})]
+           dict(type="equirectangular", **{"from": (0.5, 0.5, 0.3), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, 0.3)}),
+           dict(type="angular", angle=75.0, max_angle=50.0, projection="equisolid_angle", mirrored=True, **{"from": (0.5, 0.5, 0.3), "to": (0.45, 0.5, 1.0), "up": (0.5, 1.5, 0.3)}),
+           dict(type="angular", angle=160.0, circular=False, **{"from": (0.5, 0.5, 0.3), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, 0.3)}),
+           dict(type="angular", angle=40.0, projection="orthographic", aspect_ratio=1.3, **{"from": (0.5, 0.5, -0.8), "to": (0.5, 0.5, 1.0), "up": (0.5, 1.5, -0.8)})]
 
 
 @pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
@@ -621,6 +624,98 @@ def test_darksky_background_vs_golden_reference_render(key):
     assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.005
     p = helpers.psnr(img, ref)
     assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
+SKIES = [dict(type="sunsky", **{"from": (0.0, 0.0, 1.0)}, turbidity=2.0),                                        # sun at the zenith: atan2(0, 0) guard of phi_s
+         dict(type="sunsky", **{"from": (1.0, 0.0, 0.0)}, turbidity=9.0, power=0.7, e_var=0.2),                  # sun on the horizon
+         dict(type="sunsky", **{"from": (-0.3, 0.2, -0.9)}, turbidity=3.5, a_var=2.0, c_var=0.3),                # deep night
+         dict(type="darksky", **{"from": (0.0, 0.0, 1.0)}, turbidity=2.0, bright=0.8, exposure=0.5),
+         dict(type="darksky", **{"from": (0.6, 0.6, 0.05)}, turbidity=8.0, altitude=-0.2, color_space="CIE (D50)", power=2.0),
+         dict(type="darksky", **{"from": (-0.5, 0.1, 0.4)}, night=True, exposure=3.0, color_space="no such space", d_var=1.7)]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("sky", SKIES, ids=lambda s: s["type"] + "_" + "_".join(str(v) for v in s["from"]))
+def test_sky_models_vs_live_reference(sky):
+    """sunsky / darksky over the corners of their parameters, seen in every direction by an equirectangular camera outside the box."""
+    kw = dict(width=64, height=36, spp=2, bounces=2, background=sky,
+              camera_extra=dict(type="equirectangular", **{"from": (0.5, 0.5, -0.6), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, -0.6)}))
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    w, rgba = helpers.emu_pt_render(_assemble(**kw))
+    img = interface.normalize_film(w, rgba)
+    assert float(ref[..., :3].max()) > 0.0
+    assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max()))
+
+
+_HDR_IMG = {"filename": "tex.hdr", "color_space": "LinearRGB"}
+TEXBACKS = [dict(_image=dict(_HDR_IMG, texture={"clipping": "clip"}), type="textureback", texture="bg_tex", rotation=350.0, power=0.5),
+            dict(_image=dict(_HDR_IMG, texture={"clipping": "extend", "cropmin_x": 0.2, "cropmax_y": 0.7}), type="textureback", texture="bg_tex", mapping="probe", rotation=-30.0),
+            dict(_image=dict(_HDR_IMG, texture={"clipping": "checker", "even_tiles": True, "interpolate": "none", "xrepeat": 4, "yrepeat": 2}), type="textureback", texture="bg_tex",
+                 rotation=123.0),
+            dict(_image={"filename": "tex.tga", "color_space": "sRGB", "image_optimization": "optimized", "texture": {"adj_contrast": 1.3, "adj_mult_factor_blue": 0.6, "adj_clamp": True}},
+                 type="textureback", texture="bg_tex", mapping="angular")]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("bg", TEXBACKS, ids=["clip_rot350", "extend_crop_probe", "checker_nearest_repeat", "tga_srgb_adjusted_angular"])
+def test_texture_background_variants_vs_live_reference(bg):
+    """textureback over the texture's clipping / cropping / repeat / adjustment modes and both mappings (points clipped away are
+    black in the texture and come out as the 1e-5 floor times power)."""
+    kw = dict(width=64, height=36, spp=2, bounces=2, background=bg,
+              camera_extra=dict(type="equirectangular", **{"from": (0.5, 0.5, -0.6), "to": (0.5, 0.45, 1.0), "up": (0.5, 1.5, -0.6)}))
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec, cwd=TEST01_DIR)
+    w, rgba = helpers.emu_pt_render(_assemble(**kw))
+    img = interface.normalize_film(w, rgba)
+    assert float(ref[..., :3].max()) > 0.01
+    assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max()))
+
+
+AO_LIVE = [dict(oren_nayar=True, integrator_extra={"do_AO": True, "AO_samples": 5, "AO_distance": 0.3, "AO_color": (0.2, 0.9, 0.4, 1.0)}),
+           dict(shiny={"translucency": 0.4, "transmit_filter": 0.6}, light_samples=3, integrator_extra={"do_AO": True, "AO_samples": 1, "AO_distance": 5.0}),
+           dict(point_light=True, shiny={"specular_reflect": 0.3}, integrator_extra={"do_AO": True, "AO_samples": 2, "AO_distance": 0.2, "raydepth": 2}),
+           dict(extra_lights=("spot", "sphere"), render_extra={"adv_auto_shadow_bias_enabled": False, "adv_shadow_bias_value": 0.002},
+                integrator_extra={"do_AO": True, "AO_samples": 3, "AO_distance": 0.45})]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("cfg", AO_LIVE, ids=["oren_nayar_tinted", "translucent_one_sample", "behind_shiny_mirrors_point", "many_lights_manual_bias"])
+def test_ambient_occlusion_variants_vs_live_reference(cfg):
+    """do_AO with other BRDFs (Oren-Nayar, a translucency component next to the diffuse one), at the vertices behind mirror
+    components, after several lights, and with a manual shadow bias (the occlusion rays start at it)."""
+    kw = dict(width=64, height=36, spp=2, bounces=2, integrator="directlighting", **cfg)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    w, rgba = helpers.emu_pt_render(_assemble(**kw))
+    img = interface.normalize_film(w, rgba)
+    assert helpers.psnr(img, ref) >= 100.0, helpers.psnr(img, ref)
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max()))
+
+
+ABSORB_LIVE = [dict(glass={"objects": ("sphere", "short"), "IOR": 1.5, "absorption": (0.2, 1.0, 1.0), "absorption_dist": 0.1}, mirror={"objects": ("back",), "color": (0.9, 0.9, 0.9)},
+                    smooth_sphere=30.0, box_lift=0.013, integrator_extra={"raydepth": 5}),
+               dict(glass={"objects": ("tall",), "IOR": 1.33, "absorption": (0.7, 0.8, 0.9), "absorption_dist": 0.0}, box_lift=0.013),            # dist == 0: sigma is not scaled
+               dict(glass={"objects": ("sphere",), "IOR": 1.8, "absorption": (0.999, 0.5, 0.05), "absorption_dist": 3.0, "mirror_color": (0.6, 0.7, 0.8)}, smooth_sphere=60.0,
+                    integrator="directlighting", background=(0.2, 0.3, 0.5), integrator_extra={"raydepth": 8})]
+
+
+@pytest.mark.skipif(not helpers.have_ref("ref_render"), reason="oracle/_ref not built")
+@pytest.mark.parametrize("cfg", ABSORB_LIVE, ids=["two_glasses_and_a_mirror", "dist_zero", "deep_tree_direct"])
+def test_glass_absorption_variants_vs_live_reference(cfg):
+    kw = dict(width=64, height=36, spp=2, bounces=3, **cfg)
+    rec = helpers.ScriptRecorder()
+    scenes_pt.cornell_box(rec, **kw)
+    ref, _ = helpers.ref_render(rec)
+    w, rgba = helpers.emu_pt_render(_assemble(**kw))
+    img = interface.normalize_film(w, rgba)
+    assert helpers.psnr(img, ref) >= PSNR_MIN, helpers.psnr(img, ref)
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
