@@ -424,6 +424,8 @@ class Interface:
             if base.name in base_cache:
                 return base_cache[base.name]
             vis_o, sh_o = VIS.get(base.visibility, VIS["normal"])
+            if base.name in portal_meshes:     # BackgroundPortalLight::init: base_object_->setVisibility(Visibility::Invisible) (light_background_portal.cc:79)
+                vis_o, sh_o = False, False
             v = np.asarray(base.verts, np.float64).astype(np.float32)  # API doubles are narrowed to float (interface.cc:87)
             idx = np.asarray(base.tris, np.int64)
             words = {}
@@ -459,13 +461,16 @@ class Interface:
             base_cache[base.name] = (v, idx, f, nn, oc, uv)
             return base_cache[base.name]
 
-        # BackgroundPortalLight::init makes its mesh invisible (light_background_portal.cc:79): it only shapes the light
+        # Objects declared invisible never reach the accelerator (scene.cc:1037).  The mesh of a portal light is different: the light
+        # makes it invisible in its init(), AFTER the accelerator was built (scene.cc:218-220), so its triangles are in the tree --
+        # camera, bounce and plain shadow rays skip them (object visibility), but with transpShad the reference's intersectTs looks at
+        # the MATERIAL's visibility only (accelerator_kdtree.cc:1022) and they block (or filter) those shadow rays
         portal_meshes = {str(p.get("object_name", "")) for p in self.lights.values() if p.get("type") == "bgPortalLight"}
         for name in sorted(self.objects):
             o = self.objects[name]
             base = self.objects[o.instance_of] if o.instance_of else o
             vis_o, sh_o = VIS.get(base.visibility, VIS["normal"])
-            if (not vis_o and not sh_o) or o.is_base or base.name in portal_meshes:
+            if (not vis_o and not sh_o) or o.is_base:
                 continue
             if not base.tris:
                 continue

@@ -198,6 +198,17 @@ PT_GOLDEN_PORTAL = {
 }
 
 
+# The portal mesh under transpShad: the light hides it after the accelerator was built, so it stays in the tree, and intersectTs
+# (material visibility only) lets it block the filtered shadow rays of the OTHER lights that shine in through the opening
+# -> pt_portal_ts.npz (emulation test only: found by differential fuzzing after the last GPU minutes of the round were spent)
+PT_GOLDEN_PORTAL_TS = {
+    "portal_mesh_blocks_filtered_shadows": dict(width=80, height=45, spp=2, bounces=2, integrator="directlighting", lamp=False, portal=1.5, light_samples=2,
+                                                extra_lights=("sun", "spot"), background=_SKY_PLAIN, integrator_extra={"transpShad": True, "shadowDepth": 3}),
+    "portal_mesh_blocks_filtered_shadows_paths": dict(width=64, height=36, spp=2, bounces=3, lamp=False, portal=1.0, pane={"transparency": 0.6, "transmit_filter": 0.8},
+                                                      background=_SKY_PLAIN, integrator_extra={"transpShad": True, "shadowDepth": 4}),
+}
+
+
 def make_portal():
     out = {}
     for key, kw in PT_GOLDEN_PORTAL.items():
@@ -206,6 +217,13 @@ def make_portal():
         out[key] = helpers.ref_render(rec)[0]
         print(key, float(out[key][..., :3].mean()), flush=True)
     np.savez_compressed(os.path.join(HERE, "pt_portal.npz"), **out)
+    out = {}
+    for key, kw in PT_GOLDEN_PORTAL_TS.items():
+        rec = helpers.ScriptRecorder()
+        scenes_pt.cornell_box(rec, **kw)
+        out[key] = helpers.ref_render(rec)[0]
+        print(key, float(out[key][..., :3].mean()), flush=True)
+    np.savez_compressed(os.path.join(HERE, "pt_portal_ts.npz"), **out)
 
 
 # `angular` camera from inside the box: every projection, the circular mask (pixels without a camera ray: black, alpha 1),

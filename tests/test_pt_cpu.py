@@ -719,6 +719,24 @@ def test_glass_absorption_variants_vs_live_reference(cfg):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+@pytest.mark.parametrize("key", ["portal_mesh_blocks_filtered_shadows", "portal_mesh_blocks_filtered_shadows_paths"])
+def test_portal_mesh_stays_a_blocker_for_filtered_shadow_rays(key):
+    """transpShad + bgPortalLight: the light hides its mesh after the accelerator was built, so the triangles are in the tree;
+    intersectTs checks the material's visibility only and lets them block the shadow rays of the other lights (the plug-in
+    keeps the primitives and re-reads the visibilities; the Python mirror used to drop the mesh -- found by differential fuzzing)."""
+    sys.path.insert(0, GOLD)
+    from make_golden_large import PT_GOLDEN_PORTAL_TS
+    ref = np.load(os.path.join(GOLD, "pt_portal_ts.npz"))[key]
+    a = _assemble(**PT_GOLDEN_PORTAL_TS[key])
+    assert int(((a["flags"] & 7) == 4).sum()) == 2          # the portal quad: neither seen nor a plain-shadow blocker, but a filtered-shadow one
+    w, rgba = helpers.emu_pt_render(a)
+    img = interface.normalize_film(w, rgba)
+    assert img.shape == ref.shape and float(ref[..., :3].mean()) > 0.01
+    p = helpers.psnr(img, ref)
+    assert p >= PSNR_MIN, p
+    assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
+
+
 def _shiny2_cfgs():
     sys.path.insert(0, GOLD)
     from make_golden_large import PT_GOLDEN_SHINY2
