@@ -5,7 +5,7 @@ are rendered by the unmodified reference and by the CPU emulation of the device 
 compile); the films must agree to 2e-5 of the brightest value.  Known non-comparable classes are avoided or skipped: pixel-centre
 samples (spp = 1 hits the box edges exactly: ties in t), boxes standing on the floor (coincident faces), and several lights + paths +
 specular levels (the light-choice replay of the test hook does not cover ray trees).
-usage: python tools/fuzz_vs_reference.py <first seed> <count>     (log of the round: profiles/r2_v16_fuzz_vs_reference.log)"""
+usage: python tools/fuzz_vs_reference.py <first seed> <count> [cornell|textures|city]     (log of the round: profiles/r2_v16_fuzz_vs_reference.log)"""
 import sys, os, random, json
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -54,12 +54,59 @@ def rnd_cfg(r):
     if r.random() < 0.25: kw["extra_lights"] = tuple(r.sample(["sun", "directional", "sphere", "spot", "spot_soft"], r.choice([1, 2])))
     if r.random() < 0.15: kw["point_light"] = True
     return kw
+def rnd_tex_cfg(r):
+    """tests/test01 (textured cubes) with random texture / texture_mapper / layer parameters."""
+    kw = dict(scene="test01", width=r.choice([96, 128]), height=r.choice([54, 72]), spp=r.choice([2, 3]), bounces=r.choice([1, 2, 3]),
+              integrator=r.choice(["pathtracing", "directlighting"]), filter_type=r.choice(["box", "gauss", "mitchell", "lanczos"]), with_uv=r.random() < 0.5)
+    te = {"clipping": r.choice(["repeat", "extend", "clip", "clipcube", "checker"]), "interpolate": r.choice(["none", "bilinear"])}
+    if te["clipping"] == "repeat": te.update({"xrepeat": r.choice([1, 2, 3]), "yrepeat": r.choice([1, 2]), "mirror_x": r.random() < 0.4, "mirror_y": r.random() < 0.4})
+    if te["clipping"] == "checker": te.update({"even_tiles": r.random() < 0.7, "odd_tiles": r.random() < 0.5, "checker_dist": r.choice([0.0, 0.2, 0.5])})
+    if r.random() < 0.3: te.update({"cropmin_x": 0.1, "cropmax_x": 0.9, "cropmin_y": 0.2, "cropmax_y": 0.8})
+    if r.random() < 0.3: te["rot90"] = True
+    if r.random() < 0.4: te.update({"adj_intensity": r.uniform(0.7, 1.4), "adj_contrast": r.uniform(0.7, 1.4), "adj_mult_factor_red": r.uniform(0.5, 1.5), "adj_clamp": r.random() < 0.5})
+    kw["texture_extra"] = te
+    me = {"texco": r.choice(["orco", "global", "uv"] if kw["with_uv"] else ["orco", "global"]), "mapping": r.choice(["plain", "cube"])}
+    if r.random() < 0.5: me.update({"scale": (r.uniform(0.4, 2.5), r.uniform(0.4, 2.5), r.uniform(0.4, 2.5)), "offset": (r.uniform(-0.4, 0.4), r.uniform(-0.4, 0.4), 0.0)})
+    if r.random() < 0.3: me.update({"proj_x": r.choice([1, 2, 3]), "proj_y": r.choice([1, 2, 3]), "proj_z": r.choice([0, 1, 2, 3])})
+    kw["mapper_extra"] = me
+    le = {"blend_mode": r.choice(["mix", "add", "multiply", "subtract", "screen", "divide", "difference", "darken", "lighten"]), "colfac": r.uniform(0.2, 1.0)}
+    if r.random() < 0.3: le["stencil"] = True
+    if r.random() < 0.3: le["negative"] = True
+    if r.random() < 0.3: le.update({"noRGB": True, "def_col": (0.9, 0.3, 0.2, 1.0)})
+    kw["layer_extra"] = le
+    return kw
+
+
+def rnd_city_cfg(r):
+    """A small instanced city (yafaray_addInstance: flat and two-level uploads give the same film)."""
+    return dict(scene="city", n_tri_target=r.choice([3000, 8000]), n_base=r.choice([2, 4]), grid=r.choice([4, 6]), tri_range=(200, 800), width=r.choice([64, 80]), height=r.choice([36, 45]),
+                spp=r.choice([2, 3]), bounces=r.choice([2, 4]), filter_type=r.choice(["box", "gauss"]), seed=r.randrange(1, 1 << 16), light_samples=r.choice([1, 2]))
+
+
 def main():
     seed0, n = int(sys.argv[1]), int(sys.argv[2])
+    family = sys.argv[3] if len(sys.argv) > 3 else "cornell"
     bad = 0
     for k in range(n):
         r = random.Random(seed0 + k)
-        kw = rnd_cfg(r)
+        kw = {"cornell": rnd_cfg, "textures": rnd_tex_cfg, "city": rnd_city_cfg}[family](r)
+        if family != "cornell":
+            try:
+                yi = interface.Interface(); yi.image_dir = TEST01
+                if family == "city": yi.device_instancing = r.choice([True, False])
+                scenes_pt.build(yi, accelerator="yafaray-b200-bvh8", **kw)
+                a = yi.assemble()
+                w, rgba = helpers.emu_pt_render(a)
+            except Y4Error as e:
+                print(seed0 + k, "refused:", str(e)[:90]); continue
+            img = interface.normalize_film(w, rgba)
+            rec = helpers.ScriptRecorder(); scenes_pt.build(rec, **kw)
+            ref, _ = helpers.ref_render(rec, cwd=TEST01)
+            d = float(np.abs(img - ref).max()); tol = 2e-5 * max(1.0, float(ref.max()))
+            ok = ref.shape == img.shape and d <= tol
+            print(seed0 + k, "ok" if ok else "MISMATCH", "maxdiff %.3g tol %.3g psnr %.1f" % (d, tol, helpers.psnr(img, ref)), "" if ok else json.dumps(kw, default=str))
+            bad += 0 if ok else 1
+            continue
         try:
             yi = interface.Interface(); yi.image_dir = TEST01
             scenes_pt.cornell_box(yi, accelerator="yafaray-b200-bvh8", **kw)
