@@ -24,6 +24,22 @@ void emu_halton(uint32_t base, uint32_t start, int count, float *out)
 	Y4Halton h = y4_halton_start(base, start);
 	for(int k = 0; k < count; ++k) out[k] = y4_halton_next(h);
 }
+// bulk versions (tests/test_sampling_bulk.py: millions of inputs against oracle/_ref/ref_kat_bulk)
+void emu_lds_bulk(const uint32_t *in, uint64_t n, double *out) { const Y4LdsTables t = tables(); for(uint64_t k = 0; k < n; ++k) out[k] = y4_lds(t, (int) in[2 * k], in[2 * k + 1]); }
+void emu_lds_loop_bulk(const uint32_t *in, uint64_t n, double *out) { const Y4LdsTables t = tables(); for(uint64_t k = 0; k < n; ++k) out[k] = y4_lds_loop(t, (int) in[2 * k], in[2 * k + 1]); }
+void emu_halton_bulk(const uint32_t *in, uint64_t n, float *out)
+{
+	for(uint64_t k = 0; k < n; ++k)
+	{
+		Y4Halton h = y4_halton_start(in[2 * k], in[2 * k + 1]);
+		for(int j = 0; j < 4; ++j) out[4 * k + j] = y4_halton_next(h);
+	}
+}
+void emu_halton2_at_bulk(const uint32_t *in, uint64_t n, float *out) { for(uint64_t k = 0; k < n; ++k) for(uint32_t j = 0; j < 4; ++j) out[4 * k + j] = y4_halton2_at(in[2 * k + 1], j + 1u); }
+void emu_ri_bulk(const uint32_t *in, uint64_t n, float *out)
+{
+	for(uint64_t k = 0; k < n; ++k) { out[3 * k] = y4_ri_vdc(in[2 * k], in[2 * k + 1]); out[3 * k + 1] = y4_ri_s(in[2 * k], in[2 * k + 1]); out[3 * k + 2] = y4_ri_lp(in[2 * k], in[2 * k + 1]); }
+}
 void emu_trig(float x, float *out3) { out3[0] = y4_fast_sin(x); out3[1] = y4_fast_cos(x); out3[2] = y4_fast_exp(x * 0.5f); }
 void emu_coshemi(const float *n, float s1, float s2, float *out9)
 {

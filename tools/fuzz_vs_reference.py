@@ -4,8 +4,9 @@ background types with and without their IBL light, portal, glass (with absorptio
 are rendered by the unmodified reference and by the CPU emulation of the device stages (tests/emu: the same Y4_HD source the kernels
 compile); the films must agree to 2e-5 of the brightest value.  Known non-comparable classes are avoided or skipped: pixel-centre
 samples (spp = 1 hits the box edges exactly: ties in t), boxes standing on the floor (coincident faces), and several lights + paths +
-specular levels (the light-choice replay of the test hook does not cover ray trees).
-usage: python tools/fuzz_vs_reference.py <first seed> <count> [cornell|textures|city]     (log of the round: profiles/r2_v16_fuzz_vs_reference.log)"""
+specular levels (the light-choice replay of the test hook does not cover ray trees); the adaptive family looks from off the axis
+(multi-pass renders put the first sample of every pixel on the pixel's diagonal, i.e. exactly on the symmetric view's box edges).
+usage: python tools/fuzz_vs_reference.py <first seed> <count> [cornell|textures|city|adaptive]     (log of the round: profiles/r2_v16_fuzz_vs_reference.log)"""
 import sys, os, random, json
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -83,23 +84,56 @@ def rnd_city_cfg(r):
                 spp=r.choice([2, 3]), bounces=r.choice([2, 4]), filter_type=r.choice(["box", "gauss"]), seed=r.randrange(1, 1 << 16), light_samples=r.choice([1, 2]))
 
 
+def rnd_adaptive_cfg(r):
+    """The film side: adaptive multi-pass AA with every noise-detection knob, sample clamping, depth of field with the lens shapes,
+    transparent backgrounds; one light (the pass loop is the point here)."""
+    # box / gauss only: with the negative lobes of mitchell / lanczos the reference's filtered sampling-factor layer overshoots 1 along the
+    # background's silhouette and its adaptive passes take round(n * factor) samples there (DESIGN.md, documented deviation (v))
+    kw = dict(width=r.choice([64, 80]), height=r.choice([36, 45]), spp=r.choice([1, 2, 3]), bounces=r.choice([2, 3]), box_lift=0.013,
+              filter_type=r.choice(["box", "gauss"]), aa_pixelwidth=r.choice([1.0, 1.5, 2.0, 3.0]), light_samples=r.choice([1, 2]))
+    re = {"AA_passes": r.choice([2, 3, 4]), "AA_inc_samples": r.choice([1, 2, 3]), "AA_threshold": r.choice([0.0, 0.01, 0.03, 0.1]),
+          "AA_sample_multiplier_factor": r.choice([1.0, 1.5, 2.0]), "AA_resampled_floor": r.choice([0.0, 20.0, 60.0]),
+          "AA_dark_detection_type": r.choice(["none", "linear", "curve"]), "AA_dark_threshold_factor": r.choice([0.0, 0.5, 1.0]),
+          "AA_detect_color_noise": r.random() < 0.5, "AA_variance_pixels": r.choice([0, 2, 5]), "AA_variance_edge_size": r.choice([4, 8, 10]),
+          "AA_clamp_samples": r.choice([0.0, 0.0, 0.8, 2.0])}
+    kw["render_extra"] = re
+    # an off-axis camera: with AA_passes > 1 the first sample of every pixel has dx == dy (riVdC(0, r) == riS(0, r)), which puts it exactly
+    # on the projected floor / wall edges of the symmetric default view (ties in t)
+    kw["camera_extra"] = {"from": (0.5 + r.uniform(0.02, 0.1), 0.5 - r.uniform(0.02, 0.1), -1.35), "to": (0.5, 0.5, 0.0), "up": (0.5 + r.uniform(0.02, 0.1), 1.5, -1.35)}
+    if r.random() < 0.4:
+        kw["aperture"] = r.choice([0.03, 0.08]); kw["dof_distance"] = r.choice([1.2, 1.9])
+        kw["bokeh"] = dict(bokeh_type=r.choice(["disk1", "disk2", "triangle", "square", "pentagon", "hexagon", "ring"]), bokeh_bias=r.choice(["uniform", "center", "edge"]),
+                           bokeh_rotation=r.uniform(0, 90))
+    ie = {}
+    if r.random() < 0.3: ie["bg_transp"] = True; kw["background"] = (0.2, 0.3, 0.5)
+    if r.random() < 0.3: ie["caustic_type"] = "none"
+    if ie: kw["integrator_extra"] = ie
+    if r.random() < 0.3: kw["mirror"] = {"objects": ("back",), "color": (0.9, 0.9, 0.9)}
+    if r.random() < 0.2: kw["oren_nayar"] = True
+    if r.random() < 0.2: kw["integrator"] = "directlighting"
+    return kw
+
+
 def main():
     seed0, n = int(sys.argv[1]), int(sys.argv[2])
     family = sys.argv[3] if len(sys.argv) > 3 else "cornell"
     bad = 0
     for k in range(n):
         r = random.Random(seed0 + k)
-        kw = {"cornell": rnd_cfg, "textures": rnd_tex_cfg, "city": rnd_city_cfg}[family](r)
+        kw = {"cornell": rnd_cfg, "textures": rnd_tex_cfg, "city": rnd_city_cfg, "adaptive": rnd_adaptive_cfg}[family](r)
         if family != "cornell":
             try:
                 yi = interface.Interface(); yi.image_dir = TEST01
                 if family == "city": yi.device_instancing = r.choice([True, False])
                 scenes_pt.build(yi, accelerator="yafaray-b200-bvh8", **kw)
-                a = yi.assemble()
-                w, rgba = helpers.emu_pt_render(a)
+                if family == "adaptive":
+                    img, hist = helpers.emu_adaptive_render(yi)
+                else:
+                    a = yi.assemble()
+                    w, rgba = helpers.emu_pt_render(a)
+                    img = interface.normalize_film(w, rgba)
             except Y4Error as e:
                 print(seed0 + k, "refused:", str(e)[:90]); continue
-            img = interface.normalize_film(w, rgba)
             rec = helpers.ScriptRecorder(); scenes_pt.build(rec, **kw)
             ref, _ = helpers.ref_render(rec, cwd=TEST01)
             d = float(np.abs(img - ref).max()); tol = 2e-5 * max(1.0, float(ref.max()))
