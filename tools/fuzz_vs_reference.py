@@ -6,7 +6,7 @@ compile); the films must agree to 2e-5 of the brightest value.  Known non-compar
 samples (spp = 1 hits the box edges exactly: ties in t), boxes standing on the floor (coincident faces), and several lights + paths +
 specular levels (the light-choice replay of the test hook does not cover ray trees); the adaptive family looks from off the axis
 (multi-pass renders put the first sample of every pixel on the pixel's diagonal, i.e. exactly on the symmetric view's box edges).
-usage: python tools/fuzz_vs_reference.py <first seed> <count> [cornell|textures|city|adaptive]     (log of the round: profiles/r2_v16_fuzz_vs_reference.log)"""
+usage: python tools/fuzz_vs_reference.py <first seed> <count> [cornell|textures|city|adaptive|lights|materials]     (log of the round: profiles/r2_v16_fuzz_vs_reference.log)"""
 import sys, os, random, json
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -114,18 +114,94 @@ def rnd_adaptive_cfg(r):
     return kw
 
 
+def rnd_material_cfg(r):
+    """shinydiffusemat / glass / mirror parameters over their ranges (all four shinydiffuse components, Fresnel, Oren-Nayar, emission,
+    transparent shadows through a tinted pane), one light."""
+    kw = dict(width=r.choice([48, 64]), height=r.choice([27, 36]), spp=r.choice([2, 3]), bounces=r.choice([2, 3, 4]), box_lift=0.013,
+              integrator=r.choice(["pathtracing", "directlighting"]), filter_type=r.choice(["box", "gauss"]), light_samples=r.choice([1, 2]))
+    sh = {}
+    if r.random() < 0.5: sh["specular_reflect"] = r.uniform(0.05, 0.9); sh["mirror_color"] = (r.uniform(0.5, 1), r.uniform(0.5, 1), r.uniform(0.5, 1))
+    if r.random() < 0.4: sh["transparency"] = r.uniform(0.05, 0.8); sh["transmit_filter"] = r.uniform(0.0, 1.0)
+    if r.random() < 0.4: sh["translucency"] = r.uniform(0.05, 0.8)
+    if r.random() < 0.4: sh["fresnel_effect"] = True; sh["IOR"] = r.uniform(1.1, 2.5)
+    if r.random() < 0.3: sh["diffuse_reflect"] = r.uniform(0.2, 1.0)
+    if r.random() < 0.2: sh["emit"] = r.uniform(0.05, 0.5)
+    if r.random() < 0.3: sh["diffuse_brdf"] = "oren_nayar"; sh["sigma"] = r.uniform(0.05, 0.9)
+    if sh: kw["shiny"] = sh
+    ie = {"raydepth": r.choice([1, 2, 4, 7])}
+    transp = "transparency" in sh
+    if r.random() < 0.4 and not ("fresnel_effect" in sh and "specular_reflect" in sh and transp): ie["transpShad"] = True; ie["shadowDepth"] = r.choice([1, 3, 6])
+    if r.random() < 0.2: ie["caustic_type"] = "none"
+    kw["integrator_extra"] = ie
+    m = r.random()
+    if m < 0.3:
+        kw["glass"] = {"objects": r.choice([("sphere",), ("tall",), ("short", "sphere")]), "IOR": r.uniform(1.05, 2.2), "transmit_filter": r.uniform(0, 1),
+                       "filter_color": (r.uniform(0.3, 1), r.uniform(0.3, 1), r.uniform(0.3, 1)), "mirror_color": (r.uniform(0.5, 1), r.uniform(0.5, 1), r.uniform(0.5, 1))}
+        if r.random() < 0.5: kw["glass"].update({"absorption": (r.uniform(0.05, 1), r.uniform(0.05, 1), r.uniform(0.05, 1)), "absorption_dist": r.choice([0.02, 0.2, 1.0, 5.0])})
+        kw["smooth_sphere"] = r.choice([30.0, 60.0, 180.0])
+    elif m < 0.5: kw["mirror"] = {"objects": r.choice([("back",), ("tall", "left"), ("short",)]), "color": (r.uniform(0.5, 1), r.uniform(0.5, 1), r.uniform(0.5, 1)), "reflect": r.uniform(0.3, 1.0)}
+    elif m < 0.7: kw["pane"] = {"transparency": r.uniform(0.1, 0.95), "transmit_filter": r.uniform(0, 1), "color": (r.uniform(0.2, 1), r.uniform(0.2, 1), r.uniform(0.2, 1))}
+    if r.random() < 0.3: kw["point_light"] = True
+    return kw
+
+
+class _WithLight:
+    """Forwards to an api object and creates one extra light with the given parameters right before the geometry ends."""
+    def __init__(self, api, params): self.api, self.params = api, params
+    def __getattr__(self, name): return getattr(self.api, name)
+    def endGeometry(self):
+        r = self.api.endGeometry()
+        self.api.paramsClearAll()
+        scenes_pt._set_params(self.api, self.params)
+        self.api.createLight("zz_fuzz_light")
+        return r
+
+
+def rnd_light_cfg(r):
+    """One light of a random type with random parameters lights the box (no lamp): the light constructors and samplers over their ranges."""
+    kw = dict(width=r.choice([48, 64]), height=r.choice([27, 36]), spp=r.choice([2, 3]), bounces=r.choice([1, 2, 3]), box_lift=0.013, lamp=False,
+              integrator=r.choice(["pathtracing", "directlighting"]), filter_type=r.choice(["box", "gauss"]))
+    if r.random() < 0.3: kw["mirror"] = {"objects": ("back",), "color": (0.9, 0.9, 0.9)}
+    if r.random() < 0.2: kw["oren_nayar"] = True
+    if r.random() < 0.2: kw["shiny"] = {"translucency": 0.3}
+    col = (r.uniform(0.3, 1), r.uniform(0.3, 1), r.uniform(0.3, 1), 1.0)
+    inside = (r.uniform(0.2, 0.8), r.uniform(0.5, 0.95), r.uniform(0.2, 0.8))
+    front = (r.uniform(0.1, 0.9), r.uniform(0.2, 1.2), r.uniform(-1.5, -0.3))
+    t = r.choice(["pointlight", "spotlight", "spot_soft", "spherelight", "sunlight", "directional", "directional_beam", "arealight"])
+    ns = r.choice([1, 2, 4])
+    if t == "pointlight": L = {"type": "pointlight", "from": inside, "color": col, "power": r.uniform(0.2, 1.5)}
+    elif t in ("spotlight", "spot_soft"):
+        L = {"type": "spotlight", "from": r.choice([inside, front]), "to": (r.uniform(0.2, 0.8), r.uniform(0.0, 0.5), r.uniform(0.3, 0.9)), "color": col, "power": r.uniform(0.5, 4.0),
+             "cone_angle": r.uniform(5.0, 85.0), "blend": r.choice([0.0, 0.15, 0.5, 1.0])}
+        if t == "spot_soft": L.update({"soft_shadows": True, "shadowFuzzyness": r.uniform(0.1, 1.0), "samples": ns})
+    elif t == "spherelight": L = {"type": "spherelight", "from": inside, "radius": r.uniform(0.02, 0.15), "color": col, "power": r.uniform(2.0, 20.0), "samples": ns}
+    elif t == "sunlight": L = {"type": "sunlight", "direction": (r.uniform(-0.5, 0.5), r.uniform(0.0, 0.8), -1.0), "color": col, "power": r.uniform(0.3, 1.5), "angle": r.choice([0.3, 2.0, 10.0, 85.0]), "samples": ns}
+    elif t == "directional": L = {"type": "directional", "direction": (r.uniform(-0.5, 0.5), r.uniform(0.0, 0.8), -1.0), "color": col, "power": r.uniform(0.3, 1.5)}
+    elif t == "directional_beam": L = {"type": "directional", "direction": (r.uniform(-0.2, 0.2), r.uniform(0.0, 0.4), -1.0), "infinite": False, "from": (0.5, 0.6, 0.5), "radius": r.uniform(0.1, 0.5), "color": col, "power": r.uniform(0.5, 2.0)}
+    else:
+        c = (r.uniform(0.2, 0.6), r.uniform(0.7, 0.95), r.uniform(0.2, 0.6))
+        L = {"type": "arealight", "corner": c, "point1": (c[0] + r.uniform(0.05, 0.3), c[1] + r.uniform(-0.05, 0.05), c[2]), "point2": (c[0], c[1] + r.uniform(-0.05, 0.05), c[2] + r.uniform(0.05, 0.3)),
+             "color": col, "power": r.uniform(5.0, 30.0), "samples": ns}
+    if r.random() < 0.15: L["cast_shadows"] = False
+    return kw, L
+
+
 def main():
     seed0, n = int(sys.argv[1]), int(sys.argv[2])
     family = sys.argv[3] if len(sys.argv) > 3 else "cornell"
     bad = 0
     for k in range(n):
         r = random.Random(seed0 + k)
-        kw = {"cornell": rnd_cfg, "textures": rnd_tex_cfg, "city": rnd_city_cfg, "adaptive": rnd_adaptive_cfg}[family](r)
+        kw = {"cornell": rnd_cfg, "textures": rnd_tex_cfg, "city": rnd_city_cfg, "adaptive": rnd_adaptive_cfg, "lights": rnd_light_cfg, "materials": rnd_material_cfg}[family](r)
+        wrap = lambda api: api
+        if family == "lights":
+            kw, light = kw
+            wrap = lambda api, light=light: _WithLight(api, light)
         if family != "cornell":
             try:
                 yi = interface.Interface(); yi.image_dir = TEST01
                 if family == "city": yi.device_instancing = r.choice([True, False])
-                scenes_pt.build(yi, accelerator="yafaray-b200-bvh8", **kw)
+                scenes_pt.build(wrap(yi), accelerator="yafaray-b200-bvh8", **kw)
                 if family == "adaptive":
                     img, hist = helpers.emu_adaptive_render(yi)
                 else:
@@ -134,11 +210,12 @@ def main():
                     img = interface.normalize_film(w, rgba)
             except Y4Error as e:
                 print(seed0 + k, "refused:", str(e)[:90]); continue
-            rec = helpers.ScriptRecorder(); scenes_pt.build(rec, **kw)
+            rec = helpers.ScriptRecorder(); scenes_pt.build(wrap(rec), **kw)
             ref, _ = helpers.ref_render(rec, cwd=TEST01)
             d = float(np.abs(img - ref).max()); tol = 2e-5 * max(1.0, float(ref.max()))
             ok = ref.shape == img.shape and d <= tol
-            print(seed0 + k, "ok" if ok else "MISMATCH", "maxdiff %.3g tol %.3g psnr %.1f" % (d, tol, helpers.psnr(img, ref)), "" if ok else json.dumps(kw, default=str))
+            print(seed0 + k, "ok" if ok else "MISMATCH", "maxdiff %.3g tol %.3g psnr %.1f" % (d, tol, helpers.psnr(img, ref)),
+                  "" if ok else json.dumps([kw, light] if family == "lights" else kw, default=str))
             bad += 0 if ok else 1
             continue
         try:
