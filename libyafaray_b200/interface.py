@@ -47,6 +47,9 @@ class _Mesh:
         self.matrix = None
 
 
+MAX_TWO_LEVEL_ANISOTROPY = 8.0      # largest ratio of an instance matrix's singular values the automatic two-level upload accepts
+
+
 class Interface:
     """`yafaray_Interface_t` for the GPU back end: build a scene with the C API's calls, then render()."""
 
@@ -803,6 +806,18 @@ class Interface:
             mode = env not in ("0", "false", "")
         if mode is False or not any(o.instance_of for o in self.objects.values()):
             return False
+        if mode is True:
+            return True
+        # automatic: the two-level traversal tests nodes in object space with a padding sized for similarity-like matrices (rotation,
+        # mirror, uniform or mildly non-uniform scale, shear).  Needle-like matrices (axis scales 100 : 1) lose about 1e-4 of the
+        # closest hits against the flattened scene and the reference (tools: differential fuzzing at the end of round 2), so scenes
+        # that contain one are flattened -- always possible, just larger.
+        for o in self.objects.values():
+            if o.instance_of:
+                sv = np.linalg.svd(np.asarray(o.matrix, np.float64)[:3, :3], compute_uv=False)
+                if not (sv[-1] > 0.0) or sv[0] / sv[-1] > MAX_TWO_LEVEL_ANISOTROPY:
+                    self.warnings.append(f"instance '{o.name}': axis scales {sv[0]:.3g} : {sv[-1]:.3g}; the scene is uploaded flattened")
+                    return False
         return True
 
     @property

@@ -737,6 +737,25 @@ def test_portal_mesh_stays_a_blocker_for_filtered_shadow_rays(key):
     assert np.abs(img - ref).max() <= 2e-5 * max(1.0, float(ref.max())), np.abs(img - ref).max()
 
 
+def test_automatic_two_level_upload_is_for_similarity_like_instance_matrices():
+    """Instances with needle-like matrices make the automatic mode flatten the scene (the object-space node tests of the two-level
+    traversal are padded for rotations / mirrors / near-uniform scales: found by fuzzing against the flattened scene and the kd-tree)."""
+    yi = interface.Interface()
+    scenes_pt.city(yi, n_tri_target=3000, n_base=2, grid=4, tri_range=(200, 800), width=32, height=18, spp=1, bounces=2, accelerator="yafaray-b200-bvh8")
+    assert yi._wants_two_level() and not yi.warnings
+    inst = next(o for o in yi.objects.values() if o.instance_of)
+    keep = inst.matrix.copy()
+    inst.matrix = keep @ np.diag([1.0, 0.01, 1.0, 1.0]).astype(np.float32)
+    assert not yi._wants_two_level() and "uploaded flattened" in yi.warnings[-1]
+    yi.device_instancing = True                       # an explicit request is honoured (the library still refuses singular matrices)
+    assert yi._wants_two_level()
+    yi.device_instancing = "auto"
+    inst.matrix = keep @ np.diag([-1.0, 2.0, 1.5, 1.0]).astype(np.float32)        # mirrored, mildly non-uniform: fine
+    assert yi._wants_two_level()
+    yi.device_instancing = False
+    assert not yi._wants_two_level()
+
+
 def _shiny2_cfgs():
     sys.path.insert(0, GOLD)
     from make_golden_large import PT_GOLDEN_SHINY2
