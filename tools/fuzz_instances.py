@@ -50,6 +50,11 @@ for seed in range(int(sys.argv[1]), int(sys.argv[1]) + int(sys.argv[2])):
             same = (a["prim"] == b["prim"]) & (a["t"].view(np.uint32) == b["t"].view(np.uint32)) & (a["bu"].view(np.uint32) == b["bu"].view(np.uint32)) & (a["bv"].view(np.uint32) == b["bv"].view(np.uint32))
             # exact ties in t between different primitives may resolve differently: not a difference in the surface reached
             tie = (~same) & (a["t"] == b["t"]) & (a["prim"] != b["prim"])
+            # the documented near-tie class (tests/helpers.compare_closest): two different primitives within 1e-5 of each other in t
+            near = (~same) & (a["prim"] >= 0) & (b["prim"] >= 0) & (a["prim"] != b["prim"]) & (np.abs(a["t"] - b["t"]) <= 1e-5 * np.maximum(a["t"], b["t"]))
+            n_near = int((near & ~tie).sum())
+            if n_near: print("   ", seed, "closest:", n_near, "near-ties (two primitives within 1e-5 in t: the reported t of needle-like triangles is only that accurate)")
+            tie = tie | near
             bad = int((~same & ~tie).sum())
             if bad:
                 idx = np.nonzero(~same & ~tie)[0]
